@@ -1,0 +1,345 @@
+// tcgen05 ragged paged attention for work items of up to 128 query tokens (prefill, chunked
+// continuation after an HCache restore). One CTA = one (item, query head).
+//
+//   warp 0    : TMA producer — Q tile once, then 128-token K/V tiles gathered page by page from the
+//               paged cache through the block table (2-stage ring, SWIZZLE_128B)
+//   warp 1    : TMEM allocator + tcgen05.mma issuer:  S = Q K^T (K-major x K-major),
+//               O_tile = P V (P K-major from shared memory, V MN-major straight from its page layout)
+//   warps 2-5 : softmax — one thread per query row: tcgen05.ld S, causal mask, online max/sum in
+//               registers, P -> shared (UMMA K-major swizzled layout), then O += O_tile with the
+//               running rescale kept in registers (no TMEM read-modify-write)
+//
+// Stands in for the external paged flash kernel of the reference
+// (deepspeed/inference/v2/kernels/ragged_ops/blocked_flash/blocked_flash.cpp:21-101; atoms:
+//  ragged_ops/includes/attention_atom.h:11-39).
+#include "hds_ptx.cuh"
+#include "hds_host.cuh"
+#include "../../../include/hds_b200.h"
+
+namespace hds {
+
+constexpr int kPfThreads = 192;
+constexpr int kPfTok = 128;
+constexpr int kPfStages = 2;
+
+struct PrefillArgs {
+    void* out;
+    const int32_t* block_tables;
+    const hds_attn_item* items;
+    int max_blocks_per_seq;
+    int n_q_heads, n_kv_heads, block_size;
+    float scale_log2;
+};
+
+template <int D>
+__host__ __device__ constexpr size_t pf_smem_bytes() {
+    // Q [128 x D] + P [128 x 128] + stages x (K + V) [128 x D] (16-bit) + barriers + alignment slack
+    return static_cast<size_t>(128) * D * 2 + 128 * 128 * 2 + static_cast<size_t>(kPfStages) * 2 * kPfTok * D * 2 + 256 +
+           1024;
+}
+
+template <int D, bool kBf16>
+__global__ void __launch_bounds__(kPfThreads, 1)
+paged_attn_prefill_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant__ CUtensorMap tmap_kv,
+                          const PrefillArgs a) {
+    constexpr int PANELS = D / 64;
+    constexpr int PANEL_BYTES = kPfTok * 128;  // [128 rows x 128 B]
+    constexpr int TILE_BYTES = PANELS * PANEL_BYTES;
+    constexpr uint32_t TMEM_COLS = 256;  // S: 128 columns, O_tile: D (<=128) columns
+    constexpr uint32_t IDESC_QK = make_idesc_f16(128, kPfTok, kBf16, false, false);
+    constexpr uint32_t IDESC_PV = make_idesc_f16(128, D, kBf16, false, true);  // B = V is MN-major
+
+    extern __shared__ uint8_t smem_raw[];
+    uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+    uint8_t* q_sm = smem;                         // PANELS panels of [128 x 64]
+    uint8_t* p_sm = q_sm + TILE_BYTES;            // 2 panels of [128 rows x 64 tokens]
+    uint8_t* kv_sm = p_sm + 2 * PANEL_BYTES;      // stages x (K tile, V tile)
+    uint64_t* bars = reinterpret_cast<uint64_t*>(kv_sm + kPfStages * 2 * TILE_BYTES);
+    uint64_t* q_full = bars;
+    uint64_t* kv_full = bars + 1;
+    uint64_t* kv_empty = kv_full + kPfStages;
+    uint64_t* s_full = kv_empty + kPfStages;
+    uint64_t* p_full = s_full + 1;
+    uint64_t* o_full = p_full + 1;
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(o_full + 1);
+
+    const uint32_t warp = warp_id(), lane = lane_id();
+    const hds_attn_item item = a.items[blockIdx.x];
+    const int head = blockIdx.y;
+    const int kvh = head / (a.n_q_heads / a.n_kv_heads);
+    const int kv_len = item.pos0 + item.n_q;
+    const int n_tiles = (kv_len + kPfTok - 1) / kPfTok;
+    const int bs = a.block_size;
+    const int bps = kPfTok / bs;
+
+    if (warp == 0 && lane == 0) {
+        prefetch_tmap(&tmap_q);
+        prefetch_tmap(&tmap_kv);
+        mbar_init(q_full, 1);
+        for (int i = 0; i < kPfStages; ++i) {
+            mbar_init(&kv_full[i], 1);
+            mbar_init(&kv_empty[i], 1);
+        }
+        mbar_init(s_full, 1);
+        mbar_init(p_full, 4);
+        mbar_init(o_full, 1);
+        fence_barrier_init();
+    }
+    if (warp == 1) {
+        tmem_alloc<TMEM_COLS>(tmem_slot);
+        tmem_relinquish();
+    }
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem_base = *tmem_slot;
+    const uint32_t tmem_s = tmem_base;
+    const uint32_t tmem_o = tmem_base + 128;
+
+    if (warp == 0) {
+        if (lane == 0) {
+            // ---- Q: rows q_row0 .. q_row0+127 of head `head` (rows past n_q are never stored) ----
+            mbar_expect_tx(q_full, TILE_BYTES);
+#pragma unroll
+            for (int p = 0; p < PANELS; ++p)
+                tma_load_2d(q_sm + p * PANEL_BYTES, &tmap_q, q_full, head * D + p * 64, item.q_row0, kEvictFirst);
+            // ---- K/V tiles ----
+            const int32_t* table = a.block_tables + static_cast<int64_t>(item.seq) * a.max_blocks_per_seq;
+            const int last_blk_idx = (kv_len - 1) / bs;
+            uint32_t stage = 0, phase = 0;
+            for (int ti = 0; ti < n_tiles; ++ti) {
+                mbar_wait(&kv_empty[stage], phase ^ 1);
+                uint8_t* kdst = kv_sm + stage * 2 * TILE_BYTES;
+                uint8_t* vdst = kdst + TILE_BYTES;
+                mbar_expect_tx(&kv_full[stage], 2 * TILE_BYTES);
+                for (int b = 0; b < bps; ++b) {
+                    // past the end of the sequence re-load its last page: masked out later, but keeps
+                    // every V value that meets a zero probability finite (0 * NaN would poison the row)
+                    const int bi = min(ti * bps + b, last_blk_idx);
+                    const int blk = table[bi];
+                    const int krow = ((blk * 2 + 0) * a.n_kv_heads + kvh) * bs;
+                    const int vrow = ((blk * 2 + 1) * a.n_kv_heads + kvh) * bs;
+#pragma unroll
+                    for (int p = 0; p < PANELS; ++p) {
+                        tma_load_2d(kdst + p * PANEL_BYTES + b * bs * 128, &tmap_kv, &kv_full[stage], p * 64, krow,
+                                    kEvictNormal);
+                        tma_load_2d(vdst + p * PANEL_BYTES + b * bs * 128, &tmap_kv, &kv_full[stage], p * 64, vrow,
+                                    kEvictNormal);
+                    }
+                }
+                if (++stage == kPfStages) {
+                    stage = 0;
+                    phase ^= 1;
+                }
+            }
+        }
+    } else if (warp == 1) {
+        if (lane == 0) {
+            auto issue_qk = [&](uint32_t stage) {
+                const uint8_t* ktile = kv_sm + stage * 2 * TILE_BYTES;
+#pragma unroll
+                for (int p = 0; p < PANELS; ++p) {
+                    const uint64_t dq = make_desc_kmajor_sw128(smem_u32(q_sm + p * PANEL_BYTES));
+                    const uint64_t dk = make_desc_kmajor_sw128(smem_u32(ktile + p * PANEL_BYTES));
+#pragma unroll
+                    for (int k = 0; k < 4; ++k)
+                        umma_f16_ss(tmem_s, dq + 2 * k, dk + 2 * k, IDESC_QK, (p > 0 || k > 0) ? 1u : 0u);
+                }
+                umma_commit(s_full);
+            };
+            mbar_wait(q_full, 0);
+            mbar_wait(&kv_full[0], 0);
+            tc_fence_after();
+            issue_qk(0);
+            uint32_t stage = 0, phase = 0;
+            for (int ti = 0; ti < n_tiles; ++ti) {
+                // ---- O_tile = P V for tile ti ----
+                mbar_wait(p_full, ti & 1);
+                tc_fence_after();
+                const uint8_t* vtile = kv_sm + stage * 2 * TILE_BYTES + TILE_BYTES;
+#pragma unroll
+                for (int kk = 0; kk < kPfTok / 16; ++kk) {
+                    // A = P: K-major; 16 tokens = 32 B inside the 64-token panel, 4 steps per panel
+                    const uint64_t dp =
+                        make_desc_kmajor_sw128(smem_u32(p_sm + (kk >> 2) * PANEL_BYTES)) + 2 * (kk & 3);
+                    // B = V: MN-major; 16 tokens = 16 rows of 128 B; panels of 64 dims are PANEL_BYTES apart
+                    const uint64_t dv = make_desc_mnmajor_sw128(smem_u32(vtile + kk * 16 * 128), PANEL_BYTES);
+                    umma_f16_ss(tmem_o, dp, dv, IDESC_PV, kk > 0 ? 1u : 0u);
+                }
+                umma_commit(o_full);
+                umma_commit(&kv_empty[stage]);
+                if (++stage == kPfStages) {
+                    stage = 0;
+                    phase ^= 1;
+                }
+                // ---- S for tile ti+1 overlaps the softmax threads' O merge ----
+                if (ti + 1 < n_tiles) {
+                    mbar_wait(&kv_full[stage], phase);
+                    tc_fence_after();
+                    issue_qk(stage);
+                }
+            }
+        }
+    } else {
+        // ===================== softmax / output (warps 2..5, one thread per query row) =====================
+        const uint32_t quad = warp & 3;
+        const int r = quad * 32 + lane;  // query row inside the item
+        const int q_pos = item.pos0 + r;
+        const uint32_t lane_addr = (quad * 32u) << 16;
+        float o_acc[D];
+#pragma unroll
+        for (int i = 0; i < D; ++i) o_acc[i] = 0.0f;
+        float m_run = -INFINITY, l_run = 0.0f;
+        uint8_t* p_row = p_sm + r * 128;
+        for (int ti = 0; ti < n_tiles; ++ti) {
+            const int tok0 = ti * kPfTok;
+            mbar_wait(s_full, ti & 1);
+            tc_fence_after();
+            // pass 1: row max
+            float tmax = -INFINITY;
+#pragma unroll 1
+            for (int c = 0; c < kPfTok; c += 32) {
+                uint32_t sr[32];
+                tmem_ld_32x32(tmem_s + lane_addr + c, sr);
+                tmem_ld_wait();
+#pragma unroll
+                for (int j = 0; j < 32; ++j) {
+                    const int kv_pos = tok0 + c + j;
+                    const float s = (kv_pos <= q_pos && kv_pos < kv_len) ? __uint_as_float(sr[j]) : -INFINITY;
+                    tmax = fmaxf(tmax, s);
+                }
+            }
+            const float m_new = fmaxf(m_run, tmax * a.scale_log2);
+            const float alpha = (m_run == -INFINITY) ? 0.0f : exp2f(m_run - m_new);
+            // pass 2: probabilities -> shared memory (A operand of the PV MMA)
+            float psum = 0.0f;
+#pragma unroll 1
+            for (int c = 0; c < kPfTok; c += 32) {
+                uint32_t sr[32];
+                tmem_ld_32x32(tmem_s + lane_addr + c, sr);
+                tmem_ld_wait();
+                uint32_t packed[16];
+#pragma unroll
+                for (int j = 0; j < 32; j += 2) {
+                    float p0 = 0.0f, p1 = 0.0f;
+                    const int kv0 = tok0 + c + j;
+                    if (m_new != -INFINITY) {
+                        if (kv0 <= q_pos && kv0 < kv_len) p0 = exp2f(__uint_as_float(sr[j]) * a.scale_log2 - m_new);
+                        if (kv0 + 1 <= q_pos && kv0 + 1 < kv_len)
+                            p1 = exp2f(__uint_as_float(sr[j + 1]) * a.scale_log2 - m_new);
+                    }
+                    packed[j >> 1] = pack2<kBf16>(p0, p1);
+                    // accumulate the rounded values: the MMA consumes exactly these
+                    psum += unpack_lo<kBf16>(packed[j >> 1]) + unpack_hi<kBf16>(packed[j >> 1]);
+                }
+                // 32 tokens = 4 chunks of 16 B in panel c/64, swizzled by (row & 7)
+                uint8_t* prow_panel = p_row + (c >> 6) * PANEL_BYTES;
+#pragma unroll
+                for (int q4 = 0; q4 < 4; ++q4) {
+                    const int chunk = ((c & 63) >> 3) + q4;
+                    uint4 v = make_uint4(packed[4 * q4], packed[4 * q4 + 1], packed[4 * q4 + 2], packed[4 * q4 + 3]);
+                    *reinterpret_cast<uint4*>(prow_panel + ((chunk ^ (r & 7)) << 4)) = v;
+                }
+            }
+            l_run = l_run * alpha + psum;
+            m_run = m_new;
+            // make P visible to the tensor core (async proxy), then signal the MMA warp
+            tc_fence_before();
+            fence_proxy_async_smem();
+            __syncwarp();
+            if (lane == 0) mbar_arrive(p_full);
+            // merge O_tile
+            mbar_wait(o_full, ti & 1);
+            tc_fence_after();
+#pragma unroll
+            for (int c = 0; c < D; c += 32) {
+                uint32_t orr[32];
+                tmem_ld_32x32(tmem_o + lane_addr + c, orr);
+                tmem_ld_wait();
+#pragma unroll
+                for (int j = 0; j < 32; ++j) o_acc[c + j] = o_acc[c + j] * alpha + __uint_as_float(orr[j]);
+            }
+            tc_fence_before();
+        }
+        if (r < item.n_q) {
+            const float inv = 1.0f / l_run;
+            char* dst = reinterpret_cast<char*>(a.out) +
+                        (static_cast<int64_t>(item.q_row0 + r) * a.n_q_heads + head) * D * 2;
+#pragma unroll
+            for (int c = 0; c < D; c += 8) {
+                uint4 v;
+                v.x = pack2<kBf16>(o_acc[c + 0] * inv, o_acc[c + 1] * inv);
+                v.y = pack2<kBf16>(o_acc[c + 2] * inv, o_acc[c + 3] * inv);
+                v.z = pack2<kBf16>(o_acc[c + 4] * inv, o_acc[c + 5] * inv);
+                v.w = pack2<kBf16>(o_acc[c + 6] * inv, o_acc[c + 7] * inv);
+                st_v4(dst + c * 2, v);
+            }
+        }
+    }
+
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 1) {
+        tc_fence_after();
+        tmem_dealloc<TMEM_COLS>(tmem_base);
+    }
+}
+
+template <int D, bool kBf16>
+static int launch_prefill(const CUtensorMap& tq, const CUtensorMap& tkv, const PrefillArgs& a, int n_items,
+                          cudaStream_t s) {
+    auto kern = paged_attn_prefill_kernel<D, kBf16>;
+    static bool configured[64] = {false};
+    int dev = 0;
+    cudaGetDevice(&dev);
+    if (!configured[dev & 63]) {
+        HDS_CHECK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                            static_cast<int>(pf_smem_bytes<D>())));
+        configured[dev & 63] = true;
+    }
+    dim3 grid(n_items, a.n_q_heads);
+    kern<<<grid, kPfThreads, pf_smem_bytes<D>(), s>>>(tq, tkv, a);
+    HDS_CHECK_CUDA(cudaGetLastError());
+    return HDS_OK;
+}
+
+}  // namespace hds
+
+using namespace hds;
+
+extern "C" int hds_paged_attention_prefill(const void* q, void* out, const void* kv_cache_layer, int64_t num_blocks,
+                                           const int32_t* block_tables, int max_blocks_per_seq,
+                                           const hds_attn_item* items, int n_items, int n_q_rows, int n_q_heads,
+                                           int n_kv_heads, int head_dim, int block_size, float scale, int dtype,
+                                           void* stream) {
+    HDS_REQUIRE(head_dim == 64 || head_dim == 128, "paged_attention_prefill: head_dim must be 64 or 128");
+    HDS_REQUIRE(block_size == 16 || block_size == 32 || block_size == 64 || block_size == 128,
+                "paged_attention_prefill: block_size must be 16/32/64/128");
+    HDS_REQUIRE(n_kv_heads > 0 && n_q_heads % n_kv_heads == 0, "paged_attention_prefill: n_q_heads % n_kv_heads != 0");
+    HDS_REQUIRE(dtype == 0 || dtype == 1, "paged_attention_prefill: dtype must be 0 (bf16) or 1 (fp16)");
+    if (n_items == 0) return HDS_OK;
+    PrefillArgs a;
+    memset(&a, 0, sizeof(a));
+    a.out = out;
+    a.block_tables = block_tables;
+    a.items = items;
+    a.max_blocks_per_seq = max_blocks_per_seq;
+    a.n_q_heads = n_q_heads;
+    a.n_kv_heads = n_kv_heads;
+    a.block_size = block_size;
+    a.scale_log2 = scale * 1.4426950408889634f;
+    CUtensorMap tq, tkv;
+    int rc = make_tmap_2d_16b(&tq, q, static_cast<uint64_t>(n_q_heads) * head_dim, static_cast<uint64_t>(n_q_rows),
+                              static_cast<uint64_t>(n_q_heads) * head_dim * 2, 64, 128, dtype == 0);
+    if (rc) return rc;
+    const uint64_t rows = static_cast<uint64_t>(num_blocks) * 2 * n_kv_heads * block_size;
+    rc = make_tmap_2d_16b(&tkv, kv_cache_layer, head_dim, rows, static_cast<uint64_t>(head_dim) * 2, 64, block_size,
+                          dtype == 0);
+    if (rc) return rc;
+    cudaStream_t s = static_cast<cudaStream_t>(stream);
+    if (head_dim == 128)
+        return dtype == 0 ? launch_prefill<128, true>(tq, tkv, a, n_items, s)
+                          : launch_prefill<128, false>(tq, tkv, a, n_items, s);
+    return dtype == 0 ? launch_prefill<64, true>(tq, tkv, a, n_items, s)
+                      : launch_prefill<64, false>(tq, tkv, a, n_items, s);
+}

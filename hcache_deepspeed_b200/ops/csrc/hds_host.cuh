@@ -1,0 +1,127 @@
+// Host-side helpers shared by the launchers: error plumbing, SM count, TMA descriptor encoding.
+#pragma once
+#include <cuda.h>
+#include <cuda_runtime.h>
+#include <cudaTypedefs.h>
+#include <stdint.h>
+#include <stdio.h>
+#include <string.h>
+#include <mutex>
+
+namespace hds {
+
+// Every extern "C" entry point returns 0 on success or a negative HDS error / positive cudaError_t.
+enum : int { HDS_OK = 0, HDS_ERR_BAD_ARG = -1, HDS_ERR_DRIVER = -2, HDS_ERR_UNSUPPORTED = -3, HDS_ERR_TOO_LARGE = -4 };
+
+inline thread_local char g_last_error[512] = {0};
+inline void set_error(const char* msg) {
+    strncpy(g_last_error, msg, sizeof(g_last_error) - 1);
+    g_last_error[sizeof(g_last_error) - 1] = 0;
+}
+
+#define HDS_CHECK_CUDA(expr)                                                                         \
+    do {                                                                                             \
+        cudaError_t _e = (expr);                                                                     \
+        if (_e != cudaSuccess) {                                                                     \
+            char _b[400];                                                                            \
+            snprintf(_b, sizeof(_b), "%s:%d %s -> %s", __FILE__, __LINE__, #expr, cudaGetErrorString(_e)); \
+            ::hds::set_error(_b);                                                                    \
+            return static_cast<int>(_e);                                                             \
+        }                                                                                            \
+    } while (0)
+
+#define HDS_REQUIRE(cond, msg)               \
+    do {                                     \
+        if (!(cond)) {                       \
+            ::hds::set_error(msg);           \
+            return ::hds::HDS_ERR_BAD_ARG;   \
+        }                                    \
+    } while (0)
+
+inline int sm_count() {
+    static int cached[64] = {0};
+    int dev = 0;
+    cudaGetDevice(&dev);
+    if (dev < 0 || dev >= 64) dev = 0;
+    if (cached[dev] == 0) {
+        int n = 0;
+        cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev);
+        cached[dev] = n > 0 ? n : 148;
+    }
+    return cached[dev];
+}
+
+// cuTensorMapEncodeTiled is a driver entry point; fetch it through the runtime so the library
+// does not link libcuda (the build host has no driver installed).
+inline PFN_cuTensorMapEncodeTiled_v12000 tensor_map_encoder() {
+    static PFN_cuTensorMapEncodeTiled_v12000 fn = nullptr;
+    static std::once_flag once;
+    std::call_once(once, [] {
+        void* p = nullptr;
+        cudaDriverEntryPointQueryResult q;
+        if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) == cudaSuccess &&
+            q == cudaDriverEntryPointSuccess)
+            fn = reinterpret_cast<PFN_cuTensorMapEncodeTiled_v12000>(p);
+    });
+    return fn;
+}
+
+// 2D row-major tensor [outer, inner] of 16-bit elements, row pitch in bytes; SWIZZLE_128B boxes
+// of [box_outer, box_inner] (box_inner * 2 bytes must be <= 128). OOB reads are zero-filled.
+inline int make_tmap_2d_16b(CUtensorMap* map, const void* base, uint64_t inner, uint64_t outer, uint64_t pitch_bytes,
+                            uint32_t box_inner, uint32_t box_outer, bool bf16, bool swizzle128 = true) {
+    auto enc = tensor_map_encoder();
+    if (!enc) {
+        set_error("cuTensorMapEncodeTiled unavailable (no CUDA driver?)");
+        return HDS_ERR_DRIVER;
+    }
+    if ((reinterpret_cast<uintptr_t>(base) & 15) || (pitch_bytes & 15)) {
+        set_error("TMA operand must be 16-byte aligned with a 16-byte-multiple row pitch");
+        return HDS_ERR_BAD_ARG;
+    }
+    cuuint64_t gdim[2] = {inner, outer};
+    cuuint64_t gstride[1] = {pitch_bytes};
+    cuuint32_t box[2] = {box_inner, box_outer};
+    cuuint32_t estr[2] = {1, 1};
+    CUresult r = enc(map, bf16 ? CU_TENSOR_MAP_DATA_TYPE_BFLOAT16 : CU_TENSOR_MAP_DATA_TYPE_FLOAT16, 2,
+                     const_cast<void*>(base), gdim, gstride, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                     swizzle128 ? CU_TENSOR_MAP_SWIZZLE_128B : CU_TENSOR_MAP_SWIZZLE_NONE,
+                     CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (r != CUDA_SUCCESS) {
+        char b[200];
+        snprintf(b, sizeof(b), "cuTensorMapEncodeTiled failed: CUresult %d (inner=%llu outer=%llu pitch=%llu box=%ux%u)",
+                 (int)r, (unsigned long long)inner, (unsigned long long)outer, (unsigned long long)pitch_bytes, box_inner,
+                 box_outer);
+        set_error(b);
+        return HDS_ERR_DRIVER;
+    }
+    return HDS_OK;
+}
+
+// 3D tensor [d2, d1, d0] of 16-bit elements (d0 innermost), strides in bytes for d1 and d2.
+inline int make_tmap_3d_16b(CUtensorMap* map, const void* base, uint64_t d0, uint64_t d1, uint64_t d2,
+                            uint64_t stride1_bytes, uint64_t stride2_bytes, uint32_t box0, uint32_t box1,
+                            uint32_t box2, bool bf16) {
+    auto enc = tensor_map_encoder();
+    if (!enc) {
+        set_error("cuTensorMapEncodeTiled unavailable (no CUDA driver?)");
+        return HDS_ERR_DRIVER;
+    }
+    cuuint64_t gdim[3] = {d0, d1, d2};
+    cuuint64_t gstride[2] = {stride1_bytes, stride2_bytes};
+    cuuint32_t box[3] = {box0, box1, box2};
+    cuuint32_t estr[3] = {1, 1, 1};
+    CUresult r = enc(map, bf16 ? CU_TENSOR_MAP_DATA_TYPE_BFLOAT16 : CU_TENSOR_MAP_DATA_TYPE_FLOAT16, 3,
+                     const_cast<void*>(base), gdim, gstride, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                     CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                     CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (r != CUDA_SUCCESS) {
+        char b[160];
+        snprintf(b, sizeof(b), "cuTensorMapEncodeTiled(3d) failed: CUresult %d", (int)r);
+        set_error(b);
+        return HDS_ERR_DRIVER;
+    }
+    return HDS_OK;
+}
+
+}  // namespace hds

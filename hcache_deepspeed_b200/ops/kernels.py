@@ -1,0 +1,241 @@
+"""torch-facing wrappers over the sm_100a kernel library (``include/hds_b200.h``).
+
+Every function takes CUDA tensors, launches on the current stream and returns immediately; there
+is no hidden allocation unless an ``out=`` argument is omitted. These wrappers are the ONLY way the
+framework runs compute on the device — there is no eager-PyTorch fallback behind them (the fp32
+PyTorch restatements used as test oracles live in :mod:`hcache_deepspeed_b200.ops.reference`).
+
+Reference counterparts: the ``DSKernelBase`` callables under
+``deepspeed/inference/v2/kernels/{core_ops,ragged_ops}/`` (e.g. ``core_ops/blas_kernels/blas.py``,
+``ragged_ops/linear_blocked_kv_rotary/blocked_kv_rotary.py``).
+"""
+from __future__ import annotations
+
+import ctypes
+from typing import Optional, Sequence
+
+import torch
+
+from . import native
+
+ACT_IDENTITY, ACT_GELU, ACT_RELU, ACT_SILU, ACT_GELU_TANH = 0, 1, 2, 3, 4
+ACT_CODES = {"identity": 0, None: 0, "gelu": 1, "relu": 2, "silu": 3, "gelu_tanh": 4, "gelu_new": 4,
+             "gelu_pytorch_tanh": 4, "swish": 3}
+
+EPI_STORE, EPI_GATED = 0, 1
+
+#: counts launches of our own kernels (bench.py reports it as ``gpu_launches``)
+launch_count = 0
+
+
+def _dt(t: torch.Tensor) -> int:
+    if t.dtype == torch.bfloat16:
+        return 0
+    if t.dtype == torch.float16:
+        return 1
+    raise TypeError(f"unsupported activation dtype {t.dtype}: the sm_100a kernels take bf16 or fp16")
+
+
+def _p(t: Optional[torch.Tensor]):
+    return None if t is None else t.data_ptr()
+
+
+def _stream() -> int:
+    return torch.cuda.current_stream().cuda_stream
+
+
+def _count(n: int = 1) -> None:
+    global launch_count
+    launch_count += n
+
+
+def _check_2d(t: torch.Tensor, name: str) -> None:
+    if t.dim() != 2 or t.stride(1) != 1:
+        raise ValueError(f"{name} must be 2-D with a contiguous last dimension, got {tuple(t.shape)} / {t.stride()}")
+
+
+def gemm(a: torch.Tensor, w: torch.Tensor, bias: Optional[torch.Tensor] = None, act: int = ACT_IDENTITY,
+         gated: bool = False, out: Optional[torch.Tensor] = None, bn: int = 0) -> torch.Tensor:
+    """``out = epilogue(a @ w.T + bias)`` on the tcgen05 GEMM. ``gated``: interleaved (gate, up) columns."""
+    _check_2d(a, "a")
+    _check_2d(w, "w")
+    M, K = a.shape
+    N = w.shape[0]
+    assert w.shape[1] == K and w.dtype == a.dtype
+    n_out = N // 2 if gated else N
+    if out is None:
+        out = torch.empty((M, n_out), dtype=a.dtype, device=a.device)
+    _check_2d(out, "out")
+    lib = native.cuda_lib()
+    rc = lib.hds_gemm(_p(a), a.stride(0), _p(w), w.stride(0), M, N, K, _dt(a), EPI_GATED if gated else EPI_STORE,
+                      act, _p(bias), _p(out), out.stride(0), bn, _stream())
+    native.check(rc, "hds_gemm")
+    _count()
+    return out
+
+
+def gemm_accum(a: torch.Tensor, w: torch.Tensor, accum: torch.Tensor, bias: Optional[torch.Tensor] = None,
+               peer_ptrs: Optional[Sequence[int]] = None, multicast_ptr: Optional[int] = None, bn: int = 0,
+               splits: int = 0) -> None:
+    """``accum (fp32) += a @ w.T``; with ``peer_ptrs`` / ``multicast_ptr`` the epilogue reduces into every
+    tensor-parallel rank's buffer over NVLink (fused GEMM -> all-reduce)."""
+    _check_2d(a, "a")
+    _check_2d(w, "w")
+    M, K = a.shape
+    N = w.shape[0]
+    assert accum.dtype == torch.float32 and accum.stride(-1) == 1
+    if multicast_ptr is not None:
+        ptrs, mode = [multicast_ptr], 2
+    elif peer_ptrs is not None:
+        ptrs, mode = list(peer_ptrs), 1
+    else:
+        ptrs, mode = [accum.data_ptr()], 0
+    arr = (ctypes.c_void_p * len(ptrs))(*ptrs)
+    lib = native.cuda_lib()
+    rc = lib.hds_gemm_accum(_p(a), a.stride(0), _p(w), w.stride(0), M, N, K, _dt(a), _p(bias), arr, len(ptrs), mode,
+                            accum.stride(0) if accum.dim() == 2 else N, bn, splits, _stream())
+    native.check(rc, "hds_gemm_accum")
+    _count()
+
+
+def restore_kv_proj(latents: torch.Tensor, w_kv: torch.Tensor, kv_cache_layer: torch.Tensor, tok_pos: torch.Tensor,
+                    tok_slot: torch.Tensor, inv_freq: Optional[torch.Tensor], n_kv_heads: int, head_dim: int,
+                    block_size: int, bias_kv: Optional[torch.Tensor] = None) -> None:
+    """HCache restore of one layer: K/V projection + RoPE + paged KV write in one tcgen05 kernel."""
+    _check_2d(latents, "latents")
+    T, H = latents.shape
+    lib = native.cuda_lib()
+    rc = lib.hds_restore_kv_proj(_p(latents), latents.stride(0), _p(w_kv), w_kv.stride(0), T, H, _dt(latents),
+                                 _p(bias_kv), _p(kv_cache_layer), _p(tok_pos), _p(tok_slot), _p(inv_freq), n_kv_heads,
+                                 head_dim, block_size, 0 if inv_freq is None else 1, _stream())
+    native.check(rc, "hds_restore_kv_proj")
+    _count()
+
+
+def qkv_rope_proj(x: torch.Tensor, w_qkv: torch.Tensor, q_out: torch.Tensor, kv_cache_layer: torch.Tensor,
+                  tok_pos: torch.Tensor, tok_slot: torch.Tensor, inv_freq: Optional[torch.Tensor], n_q_heads: int,
+                  n_kv_heads: int, head_dim: int, block_size: int, bias_qkv: Optional[torch.Tensor] = None) -> None:
+    """Forward QKV projection with RoPE + KV-append fused into the GEMM epilogue."""
+    _check_2d(x, "x")
+    T, H = x.shape
+    lib = native.cuda_lib()
+    rc = lib.hds_qkv_rope_proj(_p(x), x.stride(0), _p(w_qkv), w_qkv.stride(0), T, H, _dt(x), _p(bias_qkv), _p(q_out),
+                               _p(kv_cache_layer), _p(tok_pos), _p(tok_slot), _p(inv_freq), n_q_heads, n_kv_heads,
+                               head_dim, block_size, 0 if inv_freq is None else 1, _stream())
+    native.check(rc, "hds_qkv_rope_proj")
+    _count()
+
+
+def norm(x: torch.Tensor, gamma: torch.Tensor, out: torch.Tensor, *, beta: Optional[torch.Tensor] = None,
+         delta: Optional[torch.Tensor] = None, zero_delta: bool = False, res_out: Optional[torch.Tensor] = None,
+         row_idx: Optional[torch.Tensor] = None, rows: Optional[int] = None, eps: float = 1e-5,
+         layer_norm: bool = False, post_norm: bool = False) -> torch.Tensor:
+    """RMSNorm / LayerNorm with fused residual add (``delta`` may be the fp32 partial-sum buffer of
+    :func:`gemm_accum`, which is consumed and optionally re-zeroed) and optional row gather."""
+    cols = x.shape[-1]
+    n = rows if rows is not None else (row_idx.numel() if row_idx is not None else x.numel() // cols)
+    lib = native.cuda_lib()
+    rc = lib.hds_norm(_p(x), x.stride(-2) if x.dim() > 1 else cols, _p(delta),
+                      1 if (delta is not None and delta.dtype == torch.float32) else 0, 1 if zero_delta else 0,
+                      _p(res_out), _p(out), out.stride(-2) if out.dim() > 1 else cols, _p(gamma), _p(beta), _p(row_idx),
+                      n, cols, eps, 1 if layer_norm else 0, 1 if post_norm else 0, _dt(x), _stream())
+    native.check(rc, "hds_norm")
+    _count()
+    return out
+
+
+def rope_kv_append(qkv: torch.Tensor, q_out: torch.Tensor, kv_cache_layer: torch.Tensor, tok_pos: torch.Tensor,
+                   tok_slot: torch.Tensor, inv_freq: Optional[torch.Tensor], n_q_heads: int, n_kv_heads: int,
+                   head_dim: int, rotary_dim: int, block_size: int) -> None:
+    _check_2d(qkv, "qkv")
+    lib = native.cuda_lib()
+    rc = lib.hds_rope_kv_append(_p(qkv), qkv.stride(0), _p(q_out), _p(kv_cache_layer), _p(tok_pos), _p(tok_slot),
+                                _p(inv_freq), qkv.shape[0], n_q_heads, n_kv_heads, head_dim, rotary_dim, block_size,
+                                0 if inv_freq is None else 1, _dt(qkv), _stream())
+    native.check(rc, "hds_rope_kv_append")
+    _count()
+
+
+def embed(ids: torch.Tensor, weight: torch.Tensor, out: torch.Tensor, pos_weight: Optional[torch.Tensor] = None,
+          tok_pos: Optional[torch.Tensor] = None, pos_offset: int = 0) -> torch.Tensor:
+    assert ids.dtype == torch.int32
+    lib = native.cuda_lib()
+    rc = lib.hds_embed(_p(ids), _p(weight), _p(pos_weight), _p(tok_pos), pos_offset,
+                       0 if pos_weight is None else pos_weight.shape[0], _p(out), ids.numel(), weight.shape[1],
+                       weight.shape[0], _dt(weight), _stream())
+    native.check(rc, "hds_embed")
+    _count()
+    return out
+
+
+def gather_rows(x: torch.Tensor, row_idx: torch.Tensor, out: torch.Tensor) -> torch.Tensor:
+    lib = native.cuda_lib()
+    rc = lib.hds_gather_rows(_p(x), _p(row_idx), _p(out), row_idx.numel(), x.shape[-1], _stream())
+    native.check(rc, "hds_gather_rows")
+    _count()
+    return out
+
+
+def argmax(logits: torch.Tensor, out_ids: Optional[torch.Tensor] = None) -> torch.Tensor:
+    _check_2d(logits, "logits")
+    if out_ids is None:
+        out_ids = torch.empty((logits.shape[0],), dtype=torch.int32, device=logits.device)
+    code = 2 if logits.dtype == torch.float32 else _dt(logits)
+    lib = native.cuda_lib()
+    rc = lib.hds_argmax(_p(logits), logits.stride(0), logits.shape[0], logits.shape[1], _p(out_ids), None, code,
+                        _stream())
+    native.check(rc, "hds_argmax")
+    _count()
+    return out_ids
+
+
+def kv_blocks_copy(cache: torch.Tensor, staging: torch.Tensor, block_ids: torch.Tensor, to_staging: bool) -> None:
+    """cache: [layers, blocks, 2, kvh, bs, d]; staging: [n_sel, layers, 2, kvh, bs, d]."""
+    n_layers = cache.shape[0]
+    block_bytes = cache[0, 0].numel() * cache.element_size()
+    layer_stride = cache.stride(0) * cache.element_size()
+    lib = native.cuda_lib()
+    rc = lib.hds_kv_blocks_copy(_p(cache), _p(staging), _p(block_ids), block_ids.numel(), n_layers, block_bytes,
+                                layer_stride, 1 if to_staging else 0, _stream())
+    native.check(rc, "hds_kv_blocks_copy")
+    _count()
+
+
+def cvt_f32(src: torch.Tensor, dst: torch.Tensor, zero_src: bool = False) -> torch.Tensor:
+    lib = native.cuda_lib()
+    rc = lib.hds_cvt_f32(_p(src), _p(dst), src.numel(), 1 if zero_src else 0, _dt(dst), _stream())
+    native.check(rc, "hds_cvt_f32")
+    _count()
+    return dst
+
+
+def splitkv_workspace_bytes(n_items: int, n_q_heads: int, n_kv_heads: int, head_dim: int, max_splits: int,
+                            rows_per_item: int) -> int:
+    return int(native.cuda_lib().hds_paged_attention_splitkv_workspace_bytes(n_items, n_q_heads, n_kv_heads, head_dim,
+                                                                             max_splits, rows_per_item))
+
+
+def paged_attention_splitkv(q: torch.Tensor, out: torch.Tensor, kv_cache_layer: torch.Tensor,
+                            block_tables: torch.Tensor, items: torch.Tensor, n_items: int, rows_per_item: int,
+                            n_q_heads: int, n_kv_heads: int, head_dim: int, block_size: int, n_splits: int,
+                            scale: float, workspace: Optional[torch.Tensor]) -> None:
+    """kv_cache_layer: [blocks, 2, kvh, bs, d]; items: int32 [n, 4] = (seq, q_row0, n_q, pos0)."""
+    lib = native.cuda_lib()
+    rc = lib.hds_paged_attention_splitkv(_p(q), _p(out), _p(kv_cache_layer), kv_cache_layer.shape[0], _p(block_tables),
+                                         block_tables.stride(0), _p(items), n_items, rows_per_item, n_q_heads,
+                                         n_kv_heads, head_dim, block_size, n_splits, scale, _p(workspace),
+                                         0 if workspace is None else workspace.numel() * workspace.element_size(),
+                                         _dt(q), _stream())
+    native.check(rc, "hds_paged_attention_splitkv")
+    _count()
+
+
+def paged_attention_prefill(q: torch.Tensor, out: torch.Tensor, kv_cache_layer: torch.Tensor,
+                            block_tables: torch.Tensor, items: torch.Tensor, n_items: int, n_q_heads: int,
+                            n_kv_heads: int, head_dim: int, block_size: int, scale: float) -> None:
+    lib = native.cuda_lib()
+    rc = lib.hds_paged_attention_prefill(_p(q), _p(out), _p(kv_cache_layer), kv_cache_layer.shape[0], _p(block_tables),
+                                         block_tables.stride(0), _p(items), n_items, q.shape[0], n_q_heads, n_kv_heads,
+                                         head_dim, block_size, scale, _dt(q), _stream())
+    native.check(rc, "hds_paged_attention_prefill")
+    _count()

@@ -1,0 +1,115 @@
+"""ctypes bindings of the two in-tree native libraries.
+
+``libhds_b200.so``  — sm_100a CUDA kernels (``include/hds_b200.h``)
+``libhds_host.so``  — host runtime: block allocator, ragged batch builder, async file IO
+                      (``include/hds_host.h``)
+
+Loading is lazy. On a machine with a GPU a missing kernel library is a hard error (the framework
+never silently falls back to eager PyTorch on the device); on a CPU-only machine the CUDA library is
+simply not needed.
+"""
+from __future__ import annotations
+
+import ctypes
+import os
+from ctypes import c_char_p, c_float, c_int, c_int32, c_int64, c_void_p
+from pathlib import Path
+from typing import Optional
+
+LIB_DIR = Path(__file__).resolve().parent / "lib"
+
+_cuda_lib: Optional[ctypes.CDLL] = None
+_host_lib: Optional[ctypes.CDLL] = None
+
+
+class NativeLibraryError(RuntimeError):
+    pass
+
+
+class HdsKernelError(RuntimeError):
+    pass
+
+
+def _declare_cuda(lib: ctypes.CDLL) -> None:
+    P, I, L, F = c_void_p, c_int, c_int64, c_float
+    lib.hds_last_error.restype = c_char_p
+    lib.hds_last_error.argtypes = []
+    sigs = {
+        "hds_gemm": [P, L, P, L, I, I, I, I, I, I, P, P, L, I, P],
+        "hds_gemm_accum": [P, L, P, L, I, I, I, I, P, P, I, I, L, I, I, P],
+        "hds_restore_kv_proj": [P, L, P, L, I, I, I, P, P, P, P, P, I, I, I, I, P],
+        "hds_qkv_rope_proj": [P, L, P, L, I, I, I, P, P, P, P, P, P, I, I, I, I, I, P],
+        "hds_norm": [P, L, P, I, I, P, P, L, P, P, P, I, I, F, I, I, I, P],
+        "hds_rope_kv_append": [P, L, P, P, P, P, P, I, I, I, I, I, I, I, I, P],
+        "hds_embed": [P, P, P, P, I, I, P, I, I, I, I, P],
+        "hds_gather_rows": [P, P, P, I, I, P],
+        "hds_argmax": [P, L, I, I, P, P, I, P],
+        "hds_kv_blocks_copy": [P, P, P, I, I, L, L, I, P],
+        "hds_cvt_f32": [P, P, L, I, I, P],
+        "hds_paged_attention_splitkv": [P, P, P, L, P, I, P, I, I, I, I, I, I, I, F, P, L, I, P],
+        "hds_paged_attention_prefill": [P, P, P, L, P, I, P, I, I, I, I, I, I, F, I, P],
+    }
+    for name, argtypes in sigs.items():
+        fn = getattr(lib, name)
+        fn.argtypes = argtypes
+        fn.restype = c_int
+    lib.hds_paged_attention_splitkv_workspace_bytes.argtypes = [I, I, I, I, I, I]
+    lib.hds_paged_attention_splitkv_workspace_bytes.restype = c_int64
+    # optional entry points (declared when present so older builds keep loading)
+    optional = {
+        "hds_tp_barrier": ([P, I, I, P], c_int),
+        "hds_memset_u32": ([P, c_int32, L, P], c_int),
+    }
+    for name, (argtypes, restype) in optional.items():
+        if hasattr(lib, name):
+            fn = getattr(lib, name)
+            fn.argtypes = argtypes
+            fn.restype = restype
+
+
+def cuda_lib(build_if_missing: bool = True) -> ctypes.CDLL:
+    """Return the loaded sm_100a kernel library (building it in-tree first if it is absent)."""
+    global _cuda_lib
+    if _cuda_lib is not None:
+        return _cuda_lib
+    path = LIB_DIR / "libhds_b200.so"
+    if not path.exists() and build_if_missing and os.environ.get("HDS_NO_AUTOBUILD") != "1":
+        from . import build
+        build.build_cuda(verbose=True)
+    if not path.exists():
+        raise NativeLibraryError(
+            f"{path} is missing: run `python -m hcache_deepspeed_b200.ops.build` (needs nvcc). "
+            "The GPU path never falls back to eager PyTorch.")
+    lib = ctypes.CDLL(str(path), mode=ctypes.RTLD_GLOBAL)
+    _declare_cuda(lib)
+    _cuda_lib = lib
+    return lib
+
+
+def cuda_lib_loaded() -> bool:
+    return _cuda_lib is not None
+
+
+def check(rc: int, what: str) -> None:
+    """Raise with the library's message when an entry point reports failure."""
+    if rc != 0:
+        msg = cuda_lib().hds_last_error()
+        raise HdsKernelError(f"{what} failed (code {rc}): {msg.decode() if msg else 'no message'}")
+
+
+def host_lib(build_if_missing: bool = True) -> ctypes.CDLL:
+    """Return the loaded host runtime library (g++-built, no CUDA dependency)."""
+    global _host_lib
+    if _host_lib is not None:
+        return _host_lib
+    path = LIB_DIR / "libhds_host.so"
+    if not path.exists() and build_if_missing and os.environ.get("HDS_NO_AUTOBUILD") != "1":
+        from . import build
+        build.build_host(verbose=True)
+    if not path.exists():
+        raise NativeLibraryError(f"{path} is missing: run `python -m hcache_deepspeed_b200.ops.build` (needs g++)")
+    lib = ctypes.CDLL(str(path))
+    from . import host_bindings
+    host_bindings.declare(lib)
+    _host_lib = lib
+    return lib

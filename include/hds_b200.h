@@ -1,0 +1,143 @@
+/* hds_b200.h — C ABI of libhds_b200.so, the sm_100a kernel library of hcache_deepspeed_b200.
+ *
+ * Conventions
+ *   - every function returns 0 on success, a positive cudaError_t, or a negative HDS error code;
+ *     hds_last_error() returns a human-readable message for the calling thread's last failure.
+ *   - `dtype`: 0 = bfloat16, 1 = float16 (activations and weights share the dtype; accumulation is fp32).
+ *   - `stream` is a cudaStream_t passed as void*; all launches are asynchronous on that stream.
+ *   - pointers are device pointers unless the parameter name says host.
+ *   - weights are [out_features, in_features] row-major (the HF / DeepSpeed layout), i.e. y = x * W^T.
+ *   - paged KV cache of ONE layer: [num_blocks][2 (K,V)][n_kv_heads][block_size][head_dim];
+ *     `tok_slot[t] = block_id * block_size + offset` addresses a token inside it (negative = skip),
+ *     `tok_pos[t]` is the token's absolute position in its sequence (RoPE angle / learned position).
+ *
+ * Citations name the reference component each entry point stands in for
+ * (paths relative to the reference's deepspeed/inference/v2/kernels/ unless stated otherwise).
+ */
+#ifndef HDS_B200_H
+#define HDS_B200_H
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+const char* hds_last_error(void);
+
+/* ---- tcgen05 GEMMs ------------------------------------------------------------------------- */
+
+/* out = epilogue(A[M,K] * W[N,K]^T + bias).  epilogue 0: act();  1: gated — columns are interleaved
+ * (gate, up) pairs, out has N/2 columns: out[:, j] = act(c[2j]) * c[2j+1].  act: 0 id, 1 gelu, 2 relu,
+ * 3 silu, 4 gelu-tanh.  bn: tile width override (0 = heuristic).
+ * Ref: core_ops/blas_kernels/blas.h:31-136 + bias_activations + gated_activations. */
+int hds_gemm(const void* A, int64_t lda, const void* W, int64_t ldw, int M, int N, int K, int dtype, int epilogue,
+             int act, const void* bias, void* out, int64_t ldo, int bn, void* stream);
+
+/* accum[M,N] (fp32) += A * W^T (+ bias once).  Split-K partial sums and tensor-parallel partial sums share
+ * this path: red_mode 0 = local red.add; 1 = red.add (system scope) into each of n_targets peer mappings of
+ * the same buffer (GEMM -> all-reduce over NVLink from inside the epilogue); 2 = multimem.red on accum_ptrs[0],
+ * an NVLS multicast address (in-switch reduction).  accum_ptrs is a HOST array of device pointers.
+ * The consumer (hds_norm with delta_is_f32) reads and re-zeroes the buffer.
+ * Ref: blas.h + the dist.all_reduce that follows it in model_implementations/llama_v2/model.py:159-169. */
+int hds_gemm_accum(const void* A, int64_t lda, const void* W, int64_t ldw, int M, int N, int K, int dtype,
+                   const void* bias, float* const* accum_ptrs, int n_targets, int red_mode, int64_t ld_accum, int bn,
+                   int splits, void* stream);
+
+/* HCache restore: latents[T,H] * [W_k; W_v]^T with RoPE on K, written straight into the paged KV blocks.
+ * w_kv rows: all K heads then all V heads (head_dim rows each). head_dim 64 or 128.
+ * Ref: model_implementations/llama_v2/model.py:222-244 (full QKV GEMM) +
+ *      ragged_ops/linear_blocked_kv_rotary/blocked_kv_rotary_cuda.cu:25-194. */
+int hds_restore_kv_proj(const void* latents, int64_t ld_latents, const void* w_kv, int64_t ldw, int T, int H,
+                        int dtype, const void* bias_kv, void* kv_cache_layer, const int32_t* tok_pos,
+                        const int32_t* tok_slot, const float* inv_freq, int n_kv_heads, int head_dim, int block_size,
+                        int do_rope, void* stream);
+
+/* Forward QKV projection with the same fused epilogue: Q (RoPE) -> q_out[T, n_q*d]; K (RoPE), V -> paged cache.
+ * w_qkv rows: Q heads, K heads, V heads. */
+int hds_qkv_rope_proj(const void* x, int64_t ldx, const void* w_qkv, int64_t ldw, int T, int H, int dtype,
+                      const void* bias_qkv, void* q_out, void* kv_cache_layer, const int32_t* tok_pos,
+                      const int32_t* tok_slot, const float* inv_freq, int n_q_heads, int n_kv_heads, int head_dim,
+                      int block_size, int do_rope, void* stream);
+
+/* ---- normalisation ------------------------------------------------------------------------- */
+
+/* y = norm(x [+ delta]) * gamma (+ beta).  layer_norm 0 = RMSNorm, 1 = LayerNorm.
+ * delta (optional): 16-bit or fp32 (delta_is_f32); zero_delta clears an fp32 delta after reading it.
+ * res_out (optional) receives x + delta (pre-norm residual) or, with post_norm, the normalised value.
+ * row_idx (optional, excludes delta): gather — row i of the output is computed from x[row_idx[i]].
+ * Ref: core_ops/cuda_rms_norm/rms_norm_cuda.cu:18-164, core_ops/cuda_layer_norm/layer_norm_cuda.cu:30-325,
+ *      ragged_ops/logits_gather/logits_gather_cuda.cu:18-50 (the gather). */
+int hds_norm(const void* x, int64_t ld_in, void* delta, int delta_is_f32, int zero_delta, void* res_out, void* out,
+             int64_t ld_out, const void* gamma, const void* beta, const int32_t* row_idx, int rows, int cols,
+             float eps, int layer_norm, int post_norm, int dtype, void* stream);
+
+/* ---- ragged helpers ------------------------------------------------------------------------ */
+
+/* Unfused RoPE (rotate-half over the first rotary_dim dims) + paged KV append from a dense qkv[T, (nq+2nkv)*d].
+ * Ref: ragged_ops/linear_blocked_kv_rotary/blocked_kv_rotary_cuda.cu:25-194. */
+int hds_rope_kv_append(const void* qkv, int64_t ld_qkv, void* q_out, void* kv_cache_layer, const int32_t* tok_pos,
+                       const int32_t* tok_slot, const float* inv_freq, int T, int n_q_heads, int n_kv_heads,
+                       int head_dim, int rotary_dim, int block_size, int do_rope, int dtype, void* stream);
+
+/* out[t] = W[ids[t]] (+ P[clamp(tok_pos[t] + pos_offset)]).  Ref: ragged_ops/embed/embed_cuda.cu:18-80. */
+int hds_embed(const int32_t* ids, const void* W, const void* P, const int32_t* tok_pos, int pos_offset, int max_pos,
+              void* out, int T, int H, int vocab, int dtype, void* stream);
+
+/* out[i] = x[row_idx[i]].  Ref: ragged_ops/logits_gather/logits_gather_cuda.cu:18-50. */
+int hds_gather_rows(const void* x, const int32_t* row_idx, void* out, int n_rows, int H, void* stream);
+
+/* Greedy sampling: arg-max per row (ties -> lowest index). dtype 0 bf16, 1 fp16, 2 fp32.  No reference
+ * counterpart: the reference leaves sampling to its caller (DeepSpeed-MII). */
+int hds_argmax(const void* logits, int64_t ld, int n_rows, int V, int32_t* out_ids, float* out_vals, int dtype,
+               void* stream);
+
+/* Copy whole KV blocks (all layers) between the paged cache and a dense staging buffer — the device half of
+ * plain KV offload / reload. Ref: ragged/kv_cache.py:166-184 (offload/restore raise NotImplementedError). */
+int hds_kv_blocks_copy(void* cache, void* staging, const int32_t* block_ids, int n_sel, int n_layers,
+                       int64_t block_bytes, int64_t layer_stride_bytes, int to_staging, void* stream);
+
+/* dst (16-bit) = src (fp32); optionally zero src. */
+int hds_cvt_f32(float* src, void* dst, int64_t n, int zero_src, int dtype, void* stream);
+
+/* ---- ragged paged attention ---------------------------------------------------------------- */
+
+/* Work item of the attention kernels (host-built by the batch scheduler, 4 x int32):
+ *   seq      index into block_tables rows
+ *   q_row0   first query token (row of q / out) of this item
+ *   n_q      query tokens in this item (consecutive rows, consecutive positions)
+ *   pos0     absolute position of the first query token; token i attends to KV positions <= pos0 + i
+ * Ref: ragged_ops/includes/attention_atom.h:11-39 + atom_builder/atom_builder.cpp:10-53. */
+typedef struct {
+    int32_t seq, q_row0, n_q, pos0;
+} hds_attn_item;
+
+/* Scratch size (bytes) hds_paged_attention_splitkv needs for n_items work items. */
+int64_t hds_paged_attention_splitkv_workspace_bytes(int n_items, int n_q_heads, int n_kv_heads, int head_dim,
+                                                    int max_splits, int rows_per_item);
+
+/* Split-KV paged attention for items with few query rows (decode, short continuations):
+ * rows_per_item = max over items of n_q * (n_q_heads / n_kv_heads), at most 8. K/V pages stream through TMA (SWIZZLE_128B) into a
+ * 3-stage shared-memory ring; partial (O, m, l) of each KV split land in `workspace`, and the last split to
+ * finish merges them (no second kernel). `workspace` must be zero-initialised once (hds_memset or cudaMemset);
+ * the kernel leaves its counters at zero again.
+ * q / out: [T, n_q_heads, head_dim]; block_tables: [n_seqs, max_blocks_per_seq] int32.
+ * Ref: the external blocked-flash kernel behind ragged_ops/blocked_flash/blocked_flash.cpp:21-101. */
+int hds_paged_attention_splitkv(const void* q, void* out, const void* kv_cache_layer, int64_t num_blocks,
+                                const int32_t* block_tables, int max_blocks_per_seq, const hds_attn_item* items,
+                                int n_items, int rows_per_item, int n_q_heads, int n_kv_heads, int head_dim,
+                                int block_size, int n_splits, float scale, void* workspace, int64_t workspace_bytes,
+                                int dtype, void* stream);
+
+/* tcgen05 paged attention for items with up to 128 query tokens (prefill / chunked continuation): QK^T and
+ * PV on the tensor cores with TMEM accumulators, TMA page gathers, online softmax in registers.
+ * n_q_rows = total rows of q (bounds the Q tensor map). The KV cache must hold finite values everywhere
+ * (allocate it zeroed): masked probabilities are exact zeros, but 0 * NaN would still poison a row. */
+int hds_paged_attention_prefill(const void* q, void* out, const void* kv_cache_layer, int64_t num_blocks,
+                                const int32_t* block_tables, int max_blocks_per_seq, const hds_attn_item* items,
+                                int n_items, int n_q_rows, int n_q_heads, int n_kv_heads, int head_dim, int block_size,
+                                float scale, int dtype, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* HDS_B200_H */

@@ -1,0 +1,318 @@
+"""Numerics of every sm_100a kernel against the fp32 PyTorch restatement of the same op
+(hcache_deepspeed_b200.ops.reference). Mirrors the reference's per-kernel tests
+(tests/unit/inference/v2/kernels/{core_ops,ragged_ops}/*, tolerances inference_test_utils.py:14-22)."""
+import math
+
+import pytest
+import torch
+
+pytestmark = [pytest.mark.gpu, pytest.mark.timeout(300)]
+
+from hcache_deepspeed_b200.ops import reference as ref  # noqa: E402
+
+DTYPES = [torch.bfloat16, torch.float16]
+
+
+def tol(dtype):
+    # bf16 has 8 bits of mantissa: one rounding of the output is 2^-8 relative
+    return dict(rtol=1.6e-2, atol=2e-2) if dtype == torch.bfloat16 else dict(rtol=4e-3, atol=4e-3)
+
+
+def K():
+    from hcache_deepspeed_b200.ops import kernels
+    return kernels
+
+
+def rand(*shape, dtype=torch.bfloat16, scale=1.0):
+    return (torch.randn(*shape, device="cuda", dtype=torch.float32) * scale).to(dtype)
+
+
+# ------------------------------------------------------------------------------------------------
+# GEMM
+# ------------------------------------------------------------------------------------------------
+@pytest.mark.parametrize("dtype", DTYPES)
+@pytest.mark.parametrize("M,N,K_,bn", [
+    (128, 256, 128, 0), (300, 520, 192, 0), (16, 4096, 4096, 0), (1, 1024, 512, 32), (77, 384, 320, 64),
+    (2048, 1024, 1024, 256), (512, 768, 2048, 128), (9, 11008 // 8 * 2, 4096, 0),
+])
+def test_gemm_store(dtype, M, N, K_, bn):
+    torch.manual_seed(0)
+    a, w = rand(M, K_, dtype=dtype), rand(N, K_, dtype=dtype, scale=K_ ** -0.5)
+    out = K().gemm(a, w, bn=bn)
+    torch.cuda.synchronize()
+    want = ref.gemm(a, w, out_dtype=torch.float32)
+    torch.testing.assert_close(out.float(), want, **tol(dtype))
+
+
+@pytest.mark.parametrize("act", [1, 2, 3, 4])
+def test_gemm_bias_act(act):
+    torch.manual_seed(1)
+    M, N, K_ = 200, 640, 256
+    a, w, b = rand(M, K_), rand(N, K_, scale=K_ ** -0.5), rand(N)
+    out = K().gemm(a, w, bias=b, act=act)
+    want = ref.gemm(a, w, bias=b, act=act, out_dtype=torch.float32)
+    torch.testing.assert_close(out.float(), want, **tol(torch.bfloat16))
+
+
+@pytest.mark.parametrize("M", [5, 128, 700])
+def test_gemm_gated(M):
+    torch.manual_seed(2)
+    N, K_ = 2 * 688, 512
+    a, w = rand(M, K_), rand(N, K_, scale=K_ ** -0.5)
+    out = K().gemm(a, w, act=3, gated=True)
+    assert out.shape == (M, N // 2)
+    want = ref.gemm(a, w, act=3, gated=True, out_dtype=torch.float32)
+    torch.testing.assert_close(out.float(), want, **tol(torch.bfloat16))
+
+
+@pytest.mark.parametrize("M,N,K_,splits", [(8, 4096, 4096, 0), (64, 512, 11008, 4), (300, 1024, 1024, 2), (16, 256, 64, 0)])
+def test_gemm_accum_splitk(M, N, K_, splits):
+    torch.manual_seed(3)
+    a, w, b = rand(M, K_), rand(N, K_, scale=K_ ** -0.5), rand(N)
+    acc = torch.zeros(M, N, device="cuda", dtype=torch.float32)
+    K().gemm_accum(a, w, acc, bias=b, splits=splits)
+    want = ref.gemm(a, w, bias=b, out_dtype=torch.float32)
+    torch.testing.assert_close(acc, want, rtol=2e-3, atol=2e-3)
+    K().gemm_accum(a, w, acc, bias=b, splits=splits)  # accumulates on top
+    torch.testing.assert_close(acc, 2 * want, rtol=2e-3, atol=4e-3)
+
+
+# ------------------------------------------------------------------------------------------------
+# norms
+# ------------------------------------------------------------------------------------------------
+@pytest.mark.parametrize("dtype", DTYPES)
+@pytest.mark.parametrize("cols", [768, 4096, 5120, 8192])
+@pytest.mark.parametrize("layer_norm", [False, True])
+def test_norm_plain(dtype, cols, layer_norm):
+    torch.manual_seed(4)
+    x, g, b = rand(37, cols, dtype=dtype), rand(cols, dtype=dtype), rand(cols, dtype=dtype)
+    out = torch.empty_like(x)
+    K().norm(x, g, out, beta=b if layer_norm else None, eps=1e-5, layer_norm=layer_norm)
+    want = ref.norm(x, g, b if layer_norm else None, 1e-5, layer_norm)
+    torch.testing.assert_close(out.float(), want.float(), **tol(dtype))
+
+
+@pytest.mark.parametrize("delta_f32", [False, True])
+@pytest.mark.parametrize("layer_norm", [False, True])
+def test_norm_residual(delta_f32, layer_norm):
+    torch.manual_seed(5)
+    rows, cols = 19, 4096
+    x, g, b = rand(rows, cols), rand(cols), rand(cols)
+    delta = torch.randn(rows, cols, device="cuda") if delta_f32 else rand(rows, cols)
+    delta_in = delta.clone()
+    res = torch.empty_like(x)
+    out = torch.empty_like(x)
+    K().norm(x, g, out, beta=b if layer_norm else None, delta=delta, zero_delta=True, res_out=res, eps=1e-6,
+             layer_norm=layer_norm)
+    want_res = (x.float() + delta_in.float()).to(torch.bfloat16)
+    want = ref.norm(want_res, g, b if layer_norm else None, 1e-6, layer_norm)
+    torch.testing.assert_close(res.float(), want_res.float(), rtol=0, atol=0)
+    torch.testing.assert_close(out.float(), want.float(), **tol(torch.bfloat16))
+    if delta_f32:
+        assert float(delta.abs().max()) == 0.0  # consumed and zeroed
+
+
+def test_norm_gather_rows():
+    torch.manual_seed(6)
+    x, g = rand(50, 2048), rand(2048)
+    idx = torch.tensor([49, 0, 7, 7, 31], device="cuda", dtype=torch.int32)
+    out = torch.empty(5, 2048, device="cuda", dtype=torch.bfloat16)
+    K().norm(x, g, out, row_idx=idx, eps=1e-5)
+    want = ref.norm(x[idx.long()], g, None, 1e-5, False)
+    torch.testing.assert_close(out.float(), want.float(), **tol(torch.bfloat16))
+
+
+# ------------------------------------------------------------------------------------------------
+# ragged helpers
+# ------------------------------------------------------------------------------------------------
+def make_cache(n_blocks, n_kv, bs, d, dtype=torch.bfloat16):
+    return torch.zeros(n_blocks, 2, n_kv, bs, d, device="cuda", dtype=dtype)
+
+
+def make_slots(T, n_blocks, bs, seed=0):
+    g = torch.Generator().manual_seed(seed)
+    perm = torch.randperm(n_blocks * bs, generator=g)[:T]
+    return perm.to(torch.int32).cuda()
+
+
+@pytest.mark.parametrize("d,rd,n_q,n_kv", [(128, 128, 4, 4), (128, 128, 8, 2), (64, 64, 12, 12), (80, 32, 4, 4), (96, 96, 2, 1)])
+def test_rope_kv_append(d, rd, n_q, n_kv):
+    torch.manual_seed(7)
+    T, bs, n_blocks = 45, 64, 6
+    qkv = rand(T, (n_q + 2 * n_kv) * d)
+    pos = torch.randint(0, 5000, (T,), device="cuda", dtype=torch.int32)
+    slot = make_slots(T, n_blocks, bs)
+    slot[3] = -1
+    inv = ref.default_inv_freq(rd, device="cuda")
+    cache = make_cache(n_blocks, n_kv, bs, d)
+    q_out = torch.empty(T, n_q * d, device="cuda", dtype=torch.bfloat16)
+    K().rope_kv_append(qkv, q_out, cache, pos, slot, inv, n_q, n_kv, d, rd, bs)
+    q, k, v = qkv.split([n_q * d, n_kv * d, n_kv * d], dim=1)
+    want_q = ref.rope_rotate_half(q.view(T, n_q, d), pos, inv, rd)
+    want_k = ref.rope_rotate_half(k.reshape(T, n_kv, d), pos, inv, rd)
+    want_cache = make_cache(n_blocks, n_kv, bs, d)
+    ref.kv_append(want_cache, want_k, v.reshape(T, n_kv, d), slot)
+    torch.testing.assert_close(q_out.view(T, n_q, d).float(), want_q.float(), **tol(torch.bfloat16))
+    torch.testing.assert_close(cache.float(), want_cache.float(), **tol(torch.bfloat16))
+
+
+def test_embed_gather_argmax_cvt():
+    torch.manual_seed(8)
+    V, H, T = 1000, 768, 33
+    W, P = rand(V, H), rand(64, H)
+    ids = torch.randint(0, V, (T,), device="cuda", dtype=torch.int32)
+    pos = torch.randint(0, 60, (T,), device="cuda", dtype=torch.int32)
+    out = torch.empty(T, H, device="cuda", dtype=torch.bfloat16)
+    K().embed(ids, W, out, pos_weight=P, tok_pos=pos, pos_offset=2)
+    want = ref.embed(ids, W, P, pos, 2)
+    torch.testing.assert_close(out.float(), want.float(), rtol=1e-2, atol=1e-2)
+    K().embed(ids, W, out)
+    torch.testing.assert_close(out, W[ids.long()], rtol=0, atol=0)
+
+    idx = torch.tensor([5, 1, 32], device="cuda", dtype=torch.int32)
+    g = torch.empty(3, H, device="cuda", dtype=torch.bfloat16)
+    K().gather_rows(out, idx, g)
+    torch.testing.assert_close(g, out[idx.long()], rtol=0, atol=0)
+
+    logits = rand(7, 32000)
+    got = K().argmax(logits)
+    assert got.tolist() == logits.float().argmax(-1).tolist()
+    lf = torch.randn(3, 50257, device="cuda")
+    assert K().argmax(lf).tolist() == lf.argmax(-1).tolist()
+
+    src = torch.randn(1000, device="cuda")
+    dst = torch.empty(1000, device="cuda", dtype=torch.bfloat16)
+    K().cvt_f32(src, dst, zero_src=True)
+    assert float(src.abs().max()) == 0.0
+
+
+def test_kv_blocks_copy_roundtrip():
+    torch.manual_seed(9)
+    L, nb, kvh, bs, d = 3, 10, 2, 64, 128
+    cache = rand(L, nb, 2, kvh, bs, d)
+    ids = torch.tensor([7, 2, 9], device="cuda", dtype=torch.int32)
+    staging = torch.empty(3, L, 2, kvh, bs, d, device="cuda", dtype=torch.bfloat16)
+    K().kv_blocks_copy(cache, staging, ids, to_staging=True)
+    want = cache[:, ids.long()].permute(1, 0, 2, 3, 4, 5)
+    torch.testing.assert_close(staging, want.contiguous(), rtol=0, atol=0)
+    cache2 = torch.zeros_like(cache)
+    K().kv_blocks_copy(cache2, staging, ids, to_staging=False)
+    torch.testing.assert_close(cache2[:, ids.long()], cache[:, ids.long()], rtol=0, atol=0)
+
+
+# ------------------------------------------------------------------------------------------------
+# fused projections (restore kernel and forward QKV)
+# ------------------------------------------------------------------------------------------------
+@pytest.mark.parametrize("dtype", DTYPES)
+@pytest.mark.parametrize("T,H,n_kv,d,rope", [(200, 512, 4, 128, True), (1000, 1024, 8, 128, True), (70, 768, 12, 64, False),
+                                             (33, 256, 2, 64, True)])
+def test_restore_kv_proj(dtype, T, H, n_kv, d, rope):
+    torch.manual_seed(10)
+    bs = 64 if d == 128 else 128
+    n_blocks = (T + bs - 1) // bs + 3
+    lat = rand(T, H, dtype=dtype)
+    w_kv = rand(2 * n_kv * d, H, dtype=dtype, scale=H ** -0.5)
+    bias = None if rope else rand(2 * n_kv * d, dtype=dtype)
+    pos = torch.arange(T, device="cuda", dtype=torch.int32) + 17
+    slot = make_slots(T, n_blocks, bs, seed=1)
+    inv = ref.default_inv_freq(d, device="cuda") if rope else None
+    cache = make_cache(n_blocks, n_kv, bs, d, dtype)
+    K().restore_kv_proj(lat, w_kv, cache, pos, slot, inv, n_kv, d, bs, bias_kv=bias)
+    kv = ref.gemm(lat, w_kv, bias=bias, out_dtype=torch.float32)
+    k, v = kv[:, :n_kv * d].view(T, n_kv, d), kv[:, n_kv * d:].view(T, n_kv, d)
+    if rope:
+        k = ref.rope_rotate_half(k, pos, inv, d)
+    want = make_cache(n_blocks, n_kv, bs, d, torch.float32)
+    ref.kv_append(want, k, v, slot)
+    torch.testing.assert_close(cache.float(), want, **tol(dtype))
+
+
+def test_qkv_rope_proj():
+    torch.manual_seed(11)
+    T, H, n_q, n_kv, d, bs = 150, 512, 4, 2, 128, 64
+    n_blocks = 5
+    x = rand(T, H)
+    w = rand((n_q + 2 * n_kv) * d, H, scale=H ** -0.5)
+    pos = torch.arange(T, device="cuda", dtype=torch.int32)
+    slot = make_slots(T, n_blocks, bs, seed=2)
+    inv = ref.default_inv_freq(d, device="cuda")
+    cache = make_cache(n_blocks, n_kv, bs, d)
+    q_out = torch.empty(T, n_q * d, device="cuda", dtype=torch.bfloat16)
+    K().qkv_rope_proj(x, w, q_out, cache, pos, slot, inv, n_q, n_kv, d, bs)
+    qkv = ref.gemm(x, w, out_dtype=torch.float32)
+    q, k, v = qkv.split([n_q * d, n_kv * d, n_kv * d], dim=1)
+    want_q = ref.rope_rotate_half(q.view(T, n_q, d), pos, inv, d)
+    want_k = ref.rope_rotate_half(k.reshape(T, n_kv, d), pos, inv, d)
+    want = make_cache(n_blocks, n_kv, bs, d, torch.float32)
+    ref.kv_append(want, want_k, v.reshape(T, n_kv, d), slot)
+    torch.testing.assert_close(q_out.view(T, n_q, d).float(), want_q, **tol(torch.bfloat16))
+    torch.testing.assert_close(cache.float(), want, **tol(torch.bfloat16))
+
+
+# ------------------------------------------------------------------------------------------------
+# paged attention
+# ------------------------------------------------------------------------------------------------
+def build_paged_problem(seq_specs, n_q_heads, n_kv, d, bs, dtype=torch.bfloat16, seed=0):
+    """seq_specs: list of (ctx_before, n_new). Returns q, cache, block_tables, items(list)."""
+    g = torch.Generator().manual_seed(seed)
+    total_blocks = sum((c + n + bs - 1) // bs for c, n in seq_specs) + 4
+    perm = torch.randperm(total_blocks, generator=g).tolist()
+    max_blocks = max((c + n + bs - 1) // bs for c, n in seq_specs)
+    cache = (torch.randn(total_blocks, 2, n_kv, bs, d, generator=g) * 0.5).to(dtype).cuda()
+    tables = torch.zeros(len(seq_specs), max_blocks, dtype=torch.int32)
+    items, row = [], 0
+    for s, (ctx, n_new) in enumerate(seq_specs):
+        nb = (ctx + n_new + bs - 1) // bs
+        tables[s, :nb] = torch.tensor([perm.pop() for _ in range(nb)], dtype=torch.int32)
+        items.append((s, row, n_new, ctx))
+        row += n_new
+    q = (torch.randn(row, n_q_heads, d, generator=g)).to(dtype).cuda()
+    return q, cache, tables.cuda(), items
+
+
+@pytest.mark.parametrize("dtype", DTYPES)
+@pytest.mark.parametrize("n_q_heads,n_kv,d,bs,n_splits", [(8, 8, 128, 64, 1), (8, 8, 128, 64, 4), (16, 2, 128, 64, 3),
+                                                         (12, 12, 64, 128, 2), (4, 4, 128, 32, 5)])
+def test_attention_splitkv_decode(dtype, n_q_heads, n_kv, d, bs, n_splits):
+    specs = [(0, 1), (5, 1), (127, 1), (128, 1), (1000, 1), (4095, 1), (333, 1)]
+    q, cache, tables, items = build_paged_problem(specs, n_q_heads, n_kv, d, bs, dtype)
+    items_t = torch.tensor(items, dtype=torch.int32, device="cuda")
+    G = n_q_heads // n_kv
+    out = torch.zeros_like(q)
+    ws_bytes = K().splitkv_workspace_bytes(len(items), n_q_heads, n_kv, d, n_splits, G)
+    ws = torch.zeros(max(ws_bytes, 16), dtype=torch.uint8, device="cuda")
+    scale = 1.0 / math.sqrt(d)
+    for _ in range(2):  # second call checks the scratch counters were left clean
+        out.zero_()
+        K().paged_attention_splitkv(q, out, cache, tables, items_t, len(items), G, n_q_heads, n_kv, d, bs, n_splits,
+                                    scale, ws)
+        want = ref.paged_attention(q, cache, tables, items_t.cpu(), n_q_heads, n_kv, scale)
+        torch.testing.assert_close(out.float(), want.float(), **tol(dtype))
+
+
+def test_attention_splitkv_multirow():
+    # short continuations: several query tokens per item (MHA: rows = tokens)
+    n_q_heads = n_kv = 4
+    d, bs = 128, 64
+    specs = [(300, 8), (0, 5), (64, 8), (2000, 3)]
+    q, cache, tables, items = build_paged_problem(specs, n_q_heads, n_kv, d, bs)
+    items_t = torch.tensor(items, dtype=torch.int32, device="cuda")
+    out = torch.zeros_like(q)
+    ws = torch.zeros(K().splitkv_workspace_bytes(len(items), n_q_heads, n_kv, d, 2, 8), dtype=torch.uint8, device="cuda")
+    scale = 1.0 / math.sqrt(d)
+    K().paged_attention_splitkv(q, out, cache, tables, items_t, len(items), 8, n_q_heads, n_kv, d, bs, 2, scale, ws)
+    want = ref.paged_attention(q, cache, tables, items_t.cpu(), n_q_heads, n_kv, scale)
+    torch.testing.assert_close(out.float(), want.float(), **tol(torch.bfloat16))
+
+
+@pytest.mark.parametrize("dtype", DTYPES)
+@pytest.mark.parametrize("n_q_heads,n_kv,d,bs", [(4, 4, 128, 64), (8, 2, 128, 64), (6, 6, 64, 128), (4, 4, 128, 16)])
+def test_attention_prefill(dtype, n_q_heads, n_kv, d, bs):
+    specs = [(0, 128), (0, 17), (100, 64), (1000, 128), (4000, 96), (63, 1), (128, 128)]
+    q, cache, tables, items = build_paged_problem(specs, n_q_heads, n_kv, d, bs, dtype, seed=3)
+    items_t = torch.tensor(items, dtype=torch.int32, device="cuda")
+    out = torch.zeros_like(q)
+    scale = 1.0 / math.sqrt(d)
+    K().paged_attention_prefill(q, out, cache, tables, items_t, len(items), n_q_heads, n_kv, d, bs, scale)
+    want = ref.paged_attention(q, cache, tables, items_t.cpu(), n_q_heads, n_kv, scale)
+    torch.testing.assert_close(out.float(), want.float(), **tol(dtype))
