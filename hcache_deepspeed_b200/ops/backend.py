@@ -1,0 +1,179 @@
+"""Two interchangeable op back ends with one signature set.
+
+``CudaOps``  — the sm_100a kernels (``ops/kernels.py``); used whenever tensors live on a GPU.
+``CpuOps``   — the PyTorch restatements (``ops/reference.py``); used for the CPU configuration
+               (``init_inference`` on CPU, CPU-only CI). Never used on a CUDA device.
+
+The model executor (:mod:`hcache_deepspeed_b200.models.transformer`) is written once against this
+interface. Both back ends write into caller-provided buffers so steady-state forwards allocate nothing
+(the role of the reference's ``empty_from`` view allocator, ``deepspeed/inference/v2/allocator.py:14-28``).
+"""
+from __future__ import annotations
+
+from typing import Optional
+
+import torch
+
+from . import reference as ref
+
+
+class CpuOps:
+    name = "cpu-reference"
+
+    # ---- linear ---------------------------------------------------------------------------------
+    def gemm(self, a, w, out, bias=None, act=0, gated=False, workspace=None):
+        out.copy_(ref.gemm(a, w, bias=bias, act=act, gated=gated))
+        return out
+
+    def gemm_accum(self, a, w, accum, bias=None, comm=None):
+        accum += ref.gemm(a, w, bias=bias, out_dtype=torch.float32)
+
+    # ---- norm -----------------------------------------------------------------------------------
+    def norm(self, x, gamma, out, beta=None, delta=None, zero_delta=False, res_out=None, eps=1e-5, layer_norm=False):
+        if delta is not None:
+            s = (x.float() + delta.float()).to(x.dtype)
+            if zero_delta and delta.dtype == torch.float32:
+                delta.zero_()
+            if res_out is not None:
+                res_out.copy_(s)
+            x = s
+        out.copy_(ref.norm(x, gamma, beta, eps, layer_norm))
+        return out
+
+    # ---- attention-side -------------------------------------------------------------------------------
+    def qkv_rope_kv_append(self, x, w_qkv, b_qkv, qkv_buf, q_out, kv_layer, tok_pos, tok_slot, inv_freq, n_q, n_kv, d,
+                           rot_dim, block_size, workspace=None):
+        T = x.shape[0]
+        qkv = ref.gemm(x, w_qkv, bias=b_qkv)
+        q, k, v = qkv.split([n_q * d, n_kv * d, n_kv * d], dim=1)
+        q, k, v = q.reshape(T, n_q, d), k.reshape(T, n_kv, d), v.reshape(T, n_kv, d)
+        if inv_freq is not None:
+            q = ref.rope_rotate_half(q, tok_pos, inv_freq, rot_dim)
+            k = ref.rope_rotate_half(k, tok_pos, inv_freq, rot_dim)
+        q_out.copy_(q.reshape(T, n_q * d))
+        ref.kv_append(kv_layer, k, v, tok_slot)
+
+    def restore_kv_proj(self, latents, w_kv, b_kv, kv_layer, tok_pos, tok_slot, inv_freq, n_kv, d, rot_dim, block_size,
+                        scratch=None):
+        T = latents.shape[0]
+        kv = ref.gemm(latents, w_kv, bias=b_kv)
+        k, v = kv[:, :n_kv * d].reshape(T, n_kv, d), kv[:, n_kv * d:].reshape(T, n_kv, d)
+        if inv_freq is not None:
+            k = ref.rope_rotate_half(k, tok_pos, inv_freq, rot_dim)
+        ref.kv_append(kv_layer, k, v, tok_slot)
+
+    def attention(self, q, out, kv_layer, batch, n_q, n_kv, d, scale, ws_small=None, ws_large=None):
+        T = q.shape[0]
+        q3, o3 = q.view(T, n_q, d), out.view(T, n_q, d)
+        for items in (batch.items_small(), batch.items_large()):
+            if items.shape[0]:
+                ref.paged_attention(q3, kv_layer, batch.block_tables(), items, n_q, n_kv, scale, out=o3)
+
+    # ---- misc ---------------------------------------------------------------------------------------
+    def embed(self, ids, weight, out, pos_weight=None, tok_pos=None, pos_offset=0):
+        out.copy_(ref.embed(ids, weight, pos_weight, tok_pos, pos_offset))
+        return out
+
+    def gather_rows(self, x, row_idx, out):
+        out.copy_(x[row_idx.long()])
+        return out
+
+    def argmax(self, logits):
+        return logits.float().argmax(-1).to(torch.int32)
+
+
+class CudaOps:
+    name = "sm_100a"
+
+    #: at or below this many tokens the QKV projection runs as split-K GEMM + RoPE/append kernel (fills all
+    #: SMs while streaming weights); above it the RoPE/KV epilogue is fused into the tcgen05 GEMM
+    FUSED_QKV_MIN_TOKENS = 129
+
+    def __init__(self):
+        from . import kernels
+        self.k = kernels
+
+    def gemm(self, a, w, out, bias=None, act=0, gated=False, workspace=None):
+        return self.k.gemm(a, w, bias=bias, act=act, gated=gated, out=out,
+                           workspace=workspace if a.shape[0] <= 128 else None)
+
+    def gemm_accum(self, a, w, accum, bias=None, comm=None):
+        if comm is not None and comm.fused:
+            self.k.gemm_accum(a, w, accum, bias=bias, peer_ptrs=comm.peer_ptrs(accum), multicast_ptr=comm.multicast_ptr(accum))
+        else:
+            self.k.gemm_accum(a, w, accum, bias=bias)
+
+    def norm(self, x, gamma, out, beta=None, delta=None, zero_delta=False, res_out=None, eps=1e-5, layer_norm=False):
+        return self.k.norm(x, gamma, out, beta=beta, delta=delta, zero_delta=zero_delta, res_out=res_out, eps=eps,
+                           layer_norm=layer_norm)
+
+    def qkv_rope_kv_append(self, x, w_qkv, b_qkv, qkv_buf, q_out, kv_layer, tok_pos, tok_slot, inv_freq, n_q, n_kv, d,
+                           rot_dim, block_size, workspace=None):
+        T = x.shape[0]
+        fusable = d in (64, 128) and (inv_freq is None or rot_dim == d)
+        if fusable and T >= self.FUSED_QKV_MIN_TOKENS:
+            self.k.qkv_rope_proj(x, w_qkv, q_out, kv_layer, tok_pos, tok_slot, inv_freq, n_q, n_kv, d, block_size,
+                                 bias_qkv=b_qkv)
+        else:
+            self.k.gemm(x, w_qkv, bias=b_qkv, out=qkv_buf, workspace=workspace if T <= 128 else None)
+            self.k.rope_kv_append(qkv_buf, q_out, kv_layer, tok_pos, tok_slot, inv_freq, n_q, n_kv, d, rot_dim, block_size)
+
+    def restore_kv_proj(self, latents, w_kv, b_kv, kv_layer, tok_pos, tok_slot, inv_freq, n_kv, d, rot_dim, block_size,
+                        scratch=None):
+        if d in (64, 128) and (inv_freq is None or rot_dim == d):
+            self.k.restore_kv_proj(latents, w_kv, kv_layer, tok_pos, tok_slot, inv_freq, n_kv, d, block_size, bias_kv=b_kv)
+        else:
+            # head sizes the fused epilogue does not cover: plain GEMM into scratch, then RoPE/append with zero
+            # query heads (scratch: [T, 2 * n_kv * d])
+            self.k.gemm(latents, w_kv, bias=b_kv, out=scratch)
+            self.k.rope_kv_append(scratch, scratch, kv_layer, tok_pos, tok_slot, inv_freq, 0, n_kv, d, rot_dim, block_size)
+
+    def attention(self, q, out, kv_layer, batch, n_q, n_kv, d, scale, ws_small=None, ws_large=None):
+        k = self.k
+        bs = batch.block_size
+        if batch.n_items_small:
+            n = batch.n_items_small
+            splits = pick_decode_splits(n, n_kv, batch.max_kv_len_small)
+            k.paged_attention_splitkv(q, out, kv_layer, batch.block_tables(), batch.items_small(), n,
+                                      batch.rows_per_small_item, n_q, n_kv, d, bs, splits, scale, ws_small)
+        if batch.n_items_large:
+            n = batch.n_items_large
+            splits = pick_prefill_splits(n, n_q, batch.max_kv_len_large)
+            k.paged_attention_prefill(q, out, kv_layer, batch.block_tables(), batch.items_large(), n, n_q, n_kv, d, bs,
+                                      scale, n_splits=splits, workspace=ws_large if splits > 1 else None)
+
+    def embed(self, ids, weight, out, pos_weight=None, tok_pos=None, pos_offset=0):
+        return self.k.embed(ids, weight, out, pos_weight=pos_weight, tok_pos=tok_pos, pos_offset=pos_offset)
+
+    def gather_rows(self, x, row_idx, out):
+        return self.k.gather_rows(x, row_idx, out)
+
+    def argmax(self, logits):
+        return self.k.argmax(logits)
+
+
+N_SM = 148
+MAX_DECODE_SPLITS = 16
+MAX_PREFILL_SPLITS = 16
+
+
+def pick_decode_splits(n_items: int, n_kv_heads: int, max_kv_len: int) -> int:
+    """KV splits for the split-KV kernel: enough CTAs for ~2 per SM, at least 2 tiles (256 keys) each."""
+    ctas = max(1, n_items * n_kv_heads)
+    want = max(1, (2 * N_SM + ctas - 1) // ctas)
+    tiles = max(1, (max_kv_len + 127) // 128)
+    return int(max(1, min(want, MAX_DECODE_SPLITS, tiles // 2 if tiles >= 2 else 1)))
+
+
+def pick_prefill_splits(n_items: int, n_q_heads: int, max_kv_len: int) -> int:
+    """KV splits for the tensor-core kernel: one CTA per SM when (items x heads) alone cannot fill the GPU."""
+    ctas = max(1, n_items * n_q_heads)
+    if ctas >= N_SM:
+        return 1
+    want = (N_SM + ctas - 1) // ctas
+    tiles = max(1, (max_kv_len + 127) // 128)
+    return int(max(1, min(want, MAX_PREFILL_SPLITS, tiles // 2 if tiles >= 2 else 1)))
+
+
+def get_ops(device: torch.device):
+    return CudaOps() if device.type == "cuda" else CpuOps()

@@ -29,7 +29,17 @@ struct PrefillArgs {
     int max_blocks_per_seq;
     int n_q_heads, n_kv_heads, block_size;
     float scale_log2;
+    int n_splits;       // KV range split over gridDim.z CTAs
+    int32_t* tickets;   // [n_items][n_q_heads][4]  (one per 32-row quadrant), zero between calls
+    float* ws_ml;       // [n_items][n_q_heads][n_splits][128][2]
+    float* ws_o;        // [n_items][n_q_heads][n_splits][128][D]
 };
+
+__device__ __forceinline__ float ex2_approx(float x) {
+    float y;
+    asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+    return y;
+}
 
 template <int D>
 __host__ __device__ constexpr size_t pf_smem_bytes() {
@@ -68,7 +78,13 @@ paged_attn_prefill_kernel(const __grid_constant__ CUtensorMap tmap_q, const __gr
     const int head = blockIdx.y;
     const int kvh = head / (a.n_q_heads / a.n_kv_heads);
     const int kv_len = item.pos0 + item.n_q;
-    const int n_tiles = (kv_len + kPfTok - 1) / kPfTok;
+    const int tiles_total = (kv_len + kPfTok - 1) / kPfTok;
+    const int tps = (tiles_total + a.n_splits - 1) / a.n_splits;
+    const int eff_splits = (tiles_total + tps - 1) / tps;
+    const int split = blockIdx.z;
+    if (split >= eff_splits) return;
+    const int t0 = split * tps;
+    const int n_tiles = min(tiles_total, t0 + tps) - t0;  // tiles of this split: absolute index t0 + ti
     const int bs = a.block_size;
     const int bps = kPfTok / bs;
 
@@ -115,7 +131,7 @@ paged_attn_prefill_kernel(const __grid_constant__ CUtensorMap tmap_q, const __gr
                 for (int b = 0; b < bps; ++b) {
                     // past the end of the sequence re-load its last page: masked out later, but keeps
                     // every V value that meets a zero probability finite (0 * NaN would poison the row)
-                    const int bi = min(ti * bps + b, last_blk_idx);
+                    const int bi = min((t0 + ti) * bps + b, last_blk_idx);
                     const int blk = table[bi];
                     const int krow = ((blk * 2 + 0) * a.n_kv_heads + kvh) * bs;
                     const int vrow = ((blk * 2 + 1) * a.n_kv_heads + kvh) * bs;
@@ -192,7 +208,10 @@ paged_attn_prefill_kernel(const __grid_constant__ CUtensorMap tmap_q, const __gr
         float m_run = -INFINITY, l_run = 0.0f;
         uint8_t* p_row = p_sm + r * 128;
         for (int ti = 0; ti < n_tiles; ++ti) {
-            const int tok0 = ti * kPfTok;
+            const int tok0 = (t0 + ti) * kPfTok;
+            // every key of this tile is visible to every query row unless the tile reaches past the
+            // first query position (rows only move the causal frontier forward) — warp-uniform
+            const bool need_mask = tok0 + kPfTok - 1 > item.pos0;
             mbar_wait(s_full, ti & 1);
             tc_fence_after();
             // pass 1: row max
@@ -202,15 +221,21 @@ paged_attn_prefill_kernel(const __grid_constant__ CUtensorMap tmap_q, const __gr
                 uint32_t sr[32];
                 tmem_ld_32x32(tmem_s + lane_addr + c, sr);
                 tmem_ld_wait();
+                if (need_mask) {
 #pragma unroll
-                for (int j = 0; j < 32; ++j) {
-                    const int kv_pos = tok0 + c + j;
-                    const float s = (kv_pos <= q_pos && kv_pos < kv_len) ? __uint_as_float(sr[j]) : -INFINITY;
-                    tmax = fmaxf(tmax, s);
+                    for (int j = 0; j < 32; ++j) {
+                        const int kv_pos = tok0 + c + j;
+                        const float sv = (kv_pos <= q_pos && kv_pos < kv_len) ? __uint_as_float(sr[j]) : -INFINITY;
+                        tmax = fmaxf(tmax, sv);
+                    }
+                } else {
+#pragma unroll
+                    for (int j = 0; j < 32; ++j) tmax = fmaxf(tmax, __uint_as_float(sr[j]));
                 }
             }
             const float m_new = fmaxf(m_run, tmax * a.scale_log2);
-            const float alpha = (m_run == -INFINITY) ? 0.0f : exp2f(m_run - m_new);
+            const float alpha = (m_run == -INFINITY) ? 0.0f : ex2_approx(m_run - m_new);
+            const float m_sub = (m_new == -INFINITY) ? 0.0f : m_new;  // fully masked row: exp2(-inf - 0) = 0
             // pass 2: probabilities -> shared memory (A operand of the PV MMA)
             float psum = 0.0f;
 #pragma unroll 1
@@ -219,18 +244,25 @@ paged_attn_prefill_kernel(const __grid_constant__ CUtensorMap tmap_q, const __gr
                 tmem_ld_32x32(tmem_s + lane_addr + c, sr);
                 tmem_ld_wait();
                 uint32_t packed[16];
+                if (need_mask) {
 #pragma unroll
-                for (int j = 0; j < 32; j += 2) {
-                    float p0 = 0.0f, p1 = 0.0f;
-                    const int kv0 = tok0 + c + j;
-                    if (m_new != -INFINITY) {
-                        if (kv0 <= q_pos && kv0 < kv_len) p0 = exp2f(__uint_as_float(sr[j]) * a.scale_log2 - m_new);
-                        if (kv0 + 1 <= q_pos && kv0 + 1 < kv_len)
-                            p1 = exp2f(__uint_as_float(sr[j + 1]) * a.scale_log2 - m_new);
+                    for (int j = 0; j < 32; j += 2) {
+                        const int kv0 = tok0 + c + j;
+                        const float s0 = (kv0 <= q_pos && kv0 < kv_len) ? __uint_as_float(sr[j]) : -INFINITY;
+                        const float s1 = (kv0 + 1 <= q_pos && kv0 + 1 < kv_len) ? __uint_as_float(sr[j + 1]) : -INFINITY;
+                        const float p0 = ex2_approx(fmaf(s0, a.scale_log2, -m_sub));
+                        const float p1 = ex2_approx(fmaf(s1, a.scale_log2, -m_sub));
+                        psum += p0 + p1;
+                        packed[j >> 1] = pack2<kBf16>(p0, p1);
                     }
-                    packed[j >> 1] = pack2<kBf16>(p0, p1);
-                    // accumulate the rounded values: the MMA consumes exactly these
-                    psum += unpack_lo<kBf16>(packed[j >> 1]) + unpack_hi<kBf16>(packed[j >> 1]);
+                } else {
+#pragma unroll
+                    for (int j = 0; j < 32; j += 2) {
+                        const float p0 = ex2_approx(fmaf(__uint_as_float(sr[j]), a.scale_log2, -m_sub));
+                        const float p1 = ex2_approx(fmaf(__uint_as_float(sr[j + 1]), a.scale_log2, -m_sub));
+                        psum += p0 + p1;
+                        packed[j >> 1] = pack2<kBf16>(p0, p1);
+                    }
                 }
                 // 32 tokens = 4 chunks of 16 B in panel c/64, swizzled by (row & 7)
                 uint8_t* prow_panel = p_row + (c >> 6) * PANEL_BYTES;
@@ -257,22 +289,77 @@ paged_attn_prefill_kernel(const __grid_constant__ CUtensorMap tmap_q, const __gr
                 tmem_ld_32x32(tmem_o + lane_addr + c, orr);
                 tmem_ld_wait();
 #pragma unroll
-                for (int j = 0; j < 32; ++j) o_acc[c + j] = o_acc[c + j] * alpha + __uint_as_float(orr[j]);
+                for (int j = 0; j < 32; ++j) o_acc[c + j] = fmaf(o_acc[c + j], alpha, __uint_as_float(orr[j]));
             }
             tc_fence_before();
         }
-        if (r < item.n_q) {
-            const float inv = 1.0f / l_run;
-            char* dst = reinterpret_cast<char*>(a.out) +
-                        (static_cast<int64_t>(item.q_row0 + r) * a.n_q_heads + head) * D * 2;
+        const bool row_valid = r < item.n_q;
+        char* dst = reinterpret_cast<char*>(a.out) + (static_cast<int64_t>(item.q_row0 + r) * a.n_q_heads + head) * D * 2;
+        if (eff_splits == 1) {
+            if (row_valid) {
+                const float inv = 1.0f / l_run;
 #pragma unroll
-            for (int c = 0; c < D; c += 8) {
-                uint4 v;
-                v.x = pack2<kBf16>(o_acc[c + 0] * inv, o_acc[c + 1] * inv);
-                v.y = pack2<kBf16>(o_acc[c + 2] * inv, o_acc[c + 3] * inv);
-                v.z = pack2<kBf16>(o_acc[c + 4] * inv, o_acc[c + 5] * inv);
-                v.w = pack2<kBf16>(o_acc[c + 6] * inv, o_acc[c + 7] * inv);
-                st_v4(dst + c * 2, v);
+                for (int c = 0; c < D; c += 8) {
+                    uint4 v;
+                    v.x = pack2<kBf16>(o_acc[c + 0] * inv, o_acc[c + 1] * inv);
+                    v.y = pack2<kBf16>(o_acc[c + 2] * inv, o_acc[c + 3] * inv);
+                    v.z = pack2<kBf16>(o_acc[c + 4] * inv, o_acc[c + 5] * inv);
+                    v.w = pack2<kBf16>(o_acc[c + 6] * inv, o_acc[c + 7] * inv);
+                    st_v4(dst + c * 2, v);
+                }
+            }
+        } else if (static_cast<int>(quad * 32) < item.n_q) {  // warp-uniform: this quadrant owns valid rows
+            // ---- split-KV: park the partial (O, m, l); the last split of this quadrant merges ----
+            const int64_t unit = static_cast<int64_t>(blockIdx.x) * a.n_q_heads + head;
+            const int64_t ws_row = (unit * a.n_splits + split) * 128 + r;
+            if (row_valid) {
+                float4* wo = reinterpret_cast<float4*>(a.ws_o + ws_row * D);
+#pragma unroll
+                for (int c = 0; c < D; c += 4) __stcg(wo + (c >> 2), make_float4(o_acc[c], o_acc[c + 1], o_acc[c + 2], o_acc[c + 3]));
+                __stcg(reinterpret_cast<float2*>(a.ws_ml + ws_row * 2), make_float2(m_run, l_run));
+            }
+            __threadfence();
+            __syncwarp();
+            int last = 0;
+            if (lane == 0) last = (atomicAdd(&a.tickets[unit * 4 + quad], 1) == eff_splits - 1) ? 1 : 0;
+            last = __shfl_sync(0xffffffffu, last, 0);
+            if (last) {
+                __threadfence();
+                if (row_valid) {
+                    float mx = -INFINITY;
+                    for (int sp = 0; sp < eff_splits; ++sp)
+                        mx = fmaxf(mx, __ldcg(a.ws_ml + ((unit * a.n_splits + sp) * 128 + r) * 2));
+                    float l_tot = 0.0f;
+#pragma unroll
+                    for (int i = 0; i < D; ++i) o_acc[i] = 0.0f;
+                    for (int sp = 0; sp < eff_splits; ++sp) {
+                        const int64_t row_sp = (unit * a.n_splits + sp) * 128 + r;
+                        const float2 ml = __ldcg(reinterpret_cast<const float2*>(a.ws_ml + row_sp * 2));
+                        const float w = (ml.x == -INFINITY) ? 0.0f : ex2_approx(ml.x - mx);
+                        l_tot = fmaf(w, ml.y, l_tot);
+                        const float4* wo = reinterpret_cast<const float4*>(a.ws_o + row_sp * D);
+#pragma unroll
+                        for (int c = 0; c < D; c += 4) {
+                            const float4 t = __ldcg(wo + (c >> 2));
+                            o_acc[c] = fmaf(w, t.x, o_acc[c]);
+                            o_acc[c + 1] = fmaf(w, t.y, o_acc[c + 1]);
+                            o_acc[c + 2] = fmaf(w, t.z, o_acc[c + 2]);
+                            o_acc[c + 3] = fmaf(w, t.w, o_acc[c + 3]);
+                        }
+                    }
+                    const float inv = 1.0f / l_tot;
+#pragma unroll
+                    for (int c = 0; c < D; c += 8) {
+                        uint4 v;
+                        v.x = pack2<kBf16>(o_acc[c + 0] * inv, o_acc[c + 1] * inv);
+                        v.y = pack2<kBf16>(o_acc[c + 2] * inv, o_acc[c + 3] * inv);
+                        v.z = pack2<kBf16>(o_acc[c + 4] * inv, o_acc[c + 5] * inv);
+                        v.w = pack2<kBf16>(o_acc[c + 6] * inv, o_acc[c + 7] * inv);
+                        st_v4(dst + c * 2, v);
+                    }
+                }
+                __syncwarp();
+                if (lane == 0) a.tickets[unit * 4 + quad] = 0;
             }
         }
     }
@@ -297,7 +384,7 @@ static int launch_prefill(const CUtensorMap& tq, const CUtensorMap& tkv, const P
                                             static_cast<int>(pf_smem_bytes<D>())));
         configured[dev & 63] = true;
     }
-    dim3 grid(n_items, a.n_q_heads);
+    dim3 grid(n_items, a.n_q_heads, a.n_splits);
     kern<<<grid, kPfThreads, pf_smem_bytes<D>(), s>>>(tq, tkv, a);
     HDS_CHECK_CUDA(cudaGetLastError());
     return HDS_OK;
@@ -307,11 +394,20 @@ static int launch_prefill(const CUtensorMap& tq, const CUtensorMap& tkv, const P
 
 using namespace hds;
 
+static inline int64_t pf_align256(int64_t x) { return (x + 255) & ~int64_t(255); }
+
+extern "C" int64_t hds_paged_attention_prefill_workspace_bytes(int n_items, int n_q_heads, int head_dim, int n_splits) {
+    if (n_splits <= 1) return 0;
+    const int64_t units = static_cast<int64_t>(n_items) * n_q_heads;
+    return pf_align256(units * 4 * 4) + pf_align256(units * n_splits * 128 * 2 * 4) +
+           pf_align256(units * n_splits * 128 * head_dim * 4);
+}
+
 extern "C" int hds_paged_attention_prefill(const void* q, void* out, const void* kv_cache_layer, int64_t num_blocks,
                                            const int32_t* block_tables, int max_blocks_per_seq,
                                            const hds_attn_item* items, int n_items, int n_q_rows, int n_q_heads,
-                                           int n_kv_heads, int head_dim, int block_size, float scale, int dtype,
-                                           void* stream) {
+                                           int n_kv_heads, int head_dim, int block_size, float scale, int n_splits,
+                                           void* workspace, int64_t workspace_bytes, int dtype, void* stream) {
     HDS_REQUIRE(head_dim == 64 || head_dim == 128, "paged_attention_prefill: head_dim must be 64 or 128");
     HDS_REQUIRE(block_size == 16 || block_size == 32 || block_size == 64 || block_size == 128,
                 "paged_attention_prefill: block_size must be 16/32/64/128");
@@ -328,6 +424,18 @@ extern "C" int hds_paged_attention_prefill(const void* q, void* out, const void*
     a.n_kv_heads = n_kv_heads;
     a.block_size = block_size;
     a.scale_log2 = scale * 1.4426950408889634f;
+    if (n_splits < 1) n_splits = 1;
+    HDS_REQUIRE(n_splits <= 64, "paged_attention_prefill: n_splits in [1,64]");
+    a.n_splits = n_splits;
+    if (n_splits > 1) {
+        const int64_t need = hds_paged_attention_prefill_workspace_bytes(n_items, n_q_heads, head_dim, n_splits);
+        HDS_REQUIRE(workspace != nullptr && workspace_bytes >= need, "paged_attention_prefill: workspace too small");
+        const int64_t units = static_cast<int64_t>(n_items) * n_q_heads;
+        char* ws = reinterpret_cast<char*>(workspace);
+        a.tickets = reinterpret_cast<int32_t*>(ws);
+        a.ws_ml = reinterpret_cast<float*>(ws + pf_align256(units * 4 * 4));
+        a.ws_o = reinterpret_cast<float*>(ws + pf_align256(units * 4 * 4) + pf_align256(units * n_splits * 128 * 2 * 4));
+    }
     CUtensorMap tq, tkv;
     int rc = make_tmap_2d_16b(&tq, q, static_cast<uint64_t>(n_q_heads) * head_dim, static_cast<uint64_t>(n_q_rows),
                               static_cast<uint64_t>(n_q_heads) * head_dim * 2, 64, 128, dtype == 0);

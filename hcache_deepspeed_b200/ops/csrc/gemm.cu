@@ -5,10 +5,10 @@
 
 namespace hds {
 
-template <int BN, int EPI, bool kBf16>
+template <int BN, int EPI, bool kBf16, int HD = 128>
 static int launch_gemm_inst(const CUtensorMap& ta, const CUtensorMap& tw, const GemmArgs& args, int grid,
                             cudaStream_t stream) {
-    auto kern = gemm_tn_kernel<BN, EPI, kBf16>;
+    auto kern = gemm_tn_kernel<BN, EPI, kBf16, HD>;
     static bool configured[64] = {false};
     int dev = 0;
     cudaGetDevice(&dev);
@@ -22,16 +22,23 @@ static int launch_gemm_inst(const CUtensorMap& ta, const CUtensorMap& tw, const 
     return HDS_OK;
 }
 
+// fused RoPE/KV epilogues: tile = BN / HD whole heads
+template <int EPI, bool kBf16>
+static int launch_gemm_rope(int bn, int hd, const CUtensorMap& ta, const CUtensorMap& tw, const GemmArgs& args,
+                            int grid, cudaStream_t stream) {
+    if (hd == 128 && bn == 128) return launch_gemm_inst<128, EPI, kBf16, 128>(ta, tw, args, grid, stream);
+    if (hd == 128 && bn == 256) return launch_gemm_inst<256, EPI, kBf16, 128>(ta, tw, args, grid, stream);
+    if (hd == 64 && bn == 64) return launch_gemm_inst<64, EPI, kBf16, 64>(ta, tw, args, grid, stream);
+    if (hd == 64 && bn == 128) return launch_gemm_inst<128, EPI, kBf16, 64>(ta, tw, args, grid, stream);
+    if (hd == 64 && bn == 256) return launch_gemm_inst<256, EPI, kBf16, 64>(ta, tw, args, grid, stream);
+    set_error("fused RoPE/KV epilogue supports head_dim 64 or 128");
+    return HDS_ERR_UNSUPPORTED;
+}
+
 template <int EPI, bool kBf16>
 static int launch_gemm_bn(int bn, const CUtensorMap& ta, const CUtensorMap& tw, const GemmArgs& args, int grid,
                           cudaStream_t stream) {
-    if constexpr (EPI == EPI_KV_ROPE || EPI == EPI_QKV_ROPE) {
-        switch (bn) {
-            case 64: return launch_gemm_inst<64, EPI, kBf16>(ta, tw, args, grid, stream);
-            case 128: return launch_gemm_inst<128, EPI, kBf16>(ta, tw, args, grid, stream);
-            default: set_error("fused RoPE/KV epilogue supports head_dim 64 or 128"); return HDS_ERR_UNSUPPORTED;
-        }
-    } else {
+    {
         switch (bn) {
             case 32: return launch_gemm_inst<32, EPI, kBf16>(ta, tw, args, grid, stream);
             case 64: return launch_gemm_inst<64, EPI, kBf16>(ta, tw, args, grid, stream);
@@ -42,23 +49,50 @@ static int launch_gemm_bn(int bn, const CUtensorMap& ta, const CUtensorMap& tw, 
     }
 }
 
-// Tile-width heuristic: cost ~ waves * BN (each CTA streams BN*K weight bytes per tile); ties go to
-// the wider tile (fewer activation re-reads).
-static int pick_bn(int M, int N, int sms, bool allow_256) {
+// Tile / split heuristic. A CTA streams (bn + a_rows) * 128 B per k-block; the critical path is
+// waves * k-blocks-per-unit of that, plus a per-unit epilogue term. Splitting K only pays when the
+// un-split tile count leaves SMs idle (decode-size M); ties go to wider tiles and fewer splits.
+struct TileCfg {
+    int bn, splits;
+};
+static TileCfg pick_config(int M, int N, int K, int sms, bool allow_split, int force_bn) {
     const int m_tiles = (M + kGemmBM - 1) / kGemmBM;
+    const int kb_total = (K + kGemmBK - 1) / kGemmBK;
+    const int a_rows = M < kGemmBM ? ((M + 7) / 8) * 8 : kGemmBM;
     const int cands[4] = {256, 128, 64, 32};
-    int best = 128;
-    long best_cost = -1;
+    TileCfg best{128, 1};
+    double best_cost = -1.0;
     for (int i = 0; i < 4; ++i) {
         const int bn = cands[i];
-        if (bn == 256 && (!allow_256 || m_tiles < 2)) continue;
-        if (bn > 32 && bn / 2 >= N) continue;
+        if (force_bn > 0 && bn != force_bn) continue;
+        if (force_bn <= 0) {
+            if (bn == 256 && m_tiles < 2) continue;
+            if (bn == 32 && N > 64) continue;  // too little in flight per SM to stream well
+            if (bn > 32 && bn / 2 >= N) continue;
+        }
         const long tiles = static_cast<long>(m_tiles) * ((N + bn - 1) / bn);
-        const long waves = (tiles + sms - 1) / sms;
-        const long cost = waves * bn;
-        if (best_cost < 0 || cost < best_cost) {
-            best_cost = cost;
-            best = bn;
+        // measured on B200: splitting K only wins when the un-split tiles cover less than half of the SMs
+        // (e.g. N=4096: 32 tiles -> 4 splits is 1.6x faster; N=12288: 96 tiles -> any split is slower)
+        int max_splits = 1;
+        if (allow_split && m_tiles == 1 && tiles * 2 <= sms) {
+            max_splits = static_cast<int>(sms / tiles);
+            if (max_splits > kb_total / 4) max_splits = kb_total / 4;
+            if (max_splits > 16) max_splits = 16;
+            if (max_splits < 1) max_splits = 1;
+        }
+        for (int sp = 1; sp <= max_splits; ++sp) {
+            const int per = (kb_total + sp - 1) / sp;
+            const int eff_sp = (kb_total + per - 1) / per;
+            const long units = tiles * eff_sp;
+            const long waves = (units + sms - 1) / sms;
+            // per-unit fixed cost ~ 6 k-blocks' worth of time (pipeline hand-off + epilogue); split units
+            // also pay the fp32 partial-sum traffic
+            const double unit_cost = per * (bn + a_rows) + 6.0 * bn + (eff_sp > 1 ? 2.0 * bn : 0.0);
+            const double cost = waves * unit_cost;
+            if (best_cost < 0 || cost < best_cost * 0.97) {
+                best_cost = cost;
+                best = TileCfg{bn, eff_sp};
+            }
         }
     }
     return best;
@@ -107,21 +141,41 @@ using namespace hds;
 
 extern "C" const char* hds_last_error(void) { return g_last_error; }
 
+static inline int64_t align256(int64_t x) { return (x + 255) & ~int64_t(255); }
+
+extern "C" int64_t hds_gemm_splitk_workspace_bytes(int M, int N) {
+    // fp32 partial sums [M, N] + tickets for up to N/32 tiles x 4 quadrants
+    return align256(static_cast<int64_t>(M) * N * 4) + align256((static_cast<int64_t>(N) / 32 + 1) * 4 * 4);
+}
+
 extern "C" int hds_gemm(const void* A, int64_t lda, const void* W, int64_t ldw, int M, int N, int K, int dtype,
-                        int epilogue, int act, const void* bias, void* out, int64_t ldo, int bn, void* stream) {
+                        int epilogue, int act, const void* bias, void* out, int64_t ldo, int bn, int splits,
+                        void* splitk_ws, int64_t splitk_ws_bytes, void* stream) {
     HDS_REQUIRE(epilogue == EPI_STORE || epilogue == EPI_GATED, "hds_gemm: epilogue must be 0 (store) or 1 (gated)");
     HDS_REQUIRE(dtype == 0 || dtype == 1, "hds_gemm: dtype must be 0 (bf16) or 1 (fp16)");
     HDS_REQUIRE(epilogue != EPI_GATED || (N % 2 == 0), "hds_gemm: gated epilogue needs an even N");
     GemmArgs g;
     memset(&g, 0, sizeof(g));
     Operands ops;
-    if (bn <= 0) bn = pick_bn(M, N, sm_count(), true);
-    int rc = prepare(g, ops, A, lda, W, ldw, M, N, K, dtype == 0, bn, 1);
+    const bool can_split = splitk_ws != nullptr && M <= kGemmBM &&
+                           splitk_ws_bytes >= hds_gemm_splitk_workspace_bytes(M, N);
+    if (splits <= 0 || bn <= 0) {
+        const TileCfg cfg = pick_config(M, N, K, sm_count(), can_split && splits <= 0, bn);
+        if (bn <= 0) bn = cfg.bn;
+        if (splits <= 0) splits = cfg.splits;
+    }
+    if (!can_split) splits = 1;
+    int rc = prepare(g, ops, A, lda, W, ldw, M, N, K, dtype == 0, bn, splits);
     if (rc) return rc;
     g.act = act;
     g.out = out;
     g.ldo = ldo;
     g.bias = bias;
+    if (g.splits > 1) {
+        g.splitk_ws = reinterpret_cast<float*>(splitk_ws);
+        g.splitk_tickets = reinterpret_cast<int32_t*>(reinterpret_cast<char*>(splitk_ws) +
+                                                      align256(static_cast<int64_t>(M) * N * 4));
+    }
     const int grid = grid_for(g, bn);
     cudaStream_t s = static_cast<cudaStream_t>(stream);
     if (dtype == 0) {
@@ -141,14 +195,10 @@ extern "C" int hds_gemm_accum(const void* A, int64_t lda, const void* W, int64_t
     GemmArgs g;
     memset(&g, 0, sizeof(g));
     Operands ops;
-    const int sms = sm_count();
-    if (bn <= 0) bn = M > kGemmBM ? pick_bn(M, N, sms, true) : (N >= 2048 ? 64 : 32);
-    if (splits <= 0) {
-        const long tiles = static_cast<long>((M + kGemmBM - 1) / kGemmBM) * ((N + bn - 1) / bn);
-        splits = static_cast<int>(sms / (tiles > 0 ? tiles : 1));
-        const int kb_total = (K + kGemmBK - 1) / kGemmBK;
-        if (splits > kb_total / 4) splits = kb_total / 4;  // keep >= 4 k-blocks (256 of K) per split
-        if (splits < 1) splits = 1;
+    if (splits <= 0 || bn <= 0) {
+        const TileCfg cfg = pick_config(M, N, K, sm_count(), splits <= 0, bn);
+        if (bn <= 0) bn = cfg.bn;
+        if (splits <= 0) splits = cfg.splits;
     }
     int rc = prepare(g, ops, A, lda, W, ldw, M, N, K, dtype == 0, bn, splits);
     if (rc) return rc;
@@ -175,7 +225,12 @@ static int gemm_rope_common(bool has_q, const void* A, int64_t lda, const void* 
     memset(&g, 0, sizeof(g));
     Operands ops;
     const int N = ((has_q ? n_q_heads : 0) + 2 * n_kv_heads) * head_dim;
-    int rc = prepare(g, ops, A, lda, W, ldw, M, N, K, dtype == 0, head_dim, 1);
+    // two (head_dim 128) or four (head_dim 64) heads per 256-wide tile once there is enough work to
+    // fill the machine with the wider tiles; otherwise one head per tile
+    const long m_tiles = (M + kGemmBM - 1) / kGemmBM;
+    int bn = head_dim;
+    if (m_tiles * ((N + 255) / 256) >= sm_count()) bn = 256;
+    int rc = prepare(g, ops, A, lda, W, ldw, M, N, K, dtype == 0, bn, 1);
     if (rc) return rc;
     g.bias = bias;
     g.q_out = q_out;
@@ -187,13 +242,13 @@ static int gemm_rope_common(bool has_q, const void* A, int64_t lda, const void* 
     g.n_kv_heads = n_kv_heads;
     g.block_size = block_size;
     g.do_rope = do_rope;
-    const int grid = grid_for(g, head_dim);
+    const int grid = grid_for(g, bn);
     cudaStream_t s = static_cast<cudaStream_t>(stream);
     if (has_q)
-        return dtype == 0 ? launch_gemm_bn<EPI_QKV_ROPE, true>(head_dim, ops.ta, ops.tw, g, grid, s)
-                          : launch_gemm_bn<EPI_QKV_ROPE, false>(head_dim, ops.ta, ops.tw, g, grid, s);
-    return dtype == 0 ? launch_gemm_bn<EPI_KV_ROPE, true>(head_dim, ops.ta, ops.tw, g, grid, s)
-                      : launch_gemm_bn<EPI_KV_ROPE, false>(head_dim, ops.ta, ops.tw, g, grid, s);
+        return dtype == 0 ? launch_gemm_rope<EPI_QKV_ROPE, true>(bn, head_dim, ops.ta, ops.tw, g, grid, s)
+                          : launch_gemm_rope<EPI_QKV_ROPE, false>(bn, head_dim, ops.ta, ops.tw, g, grid, s);
+    return dtype == 0 ? launch_gemm_rope<EPI_KV_ROPE, true>(bn, head_dim, ops.ta, ops.tw, g, grid, s)
+                      : launch_gemm_rope<EPI_KV_ROPE, false>(bn, head_dim, ops.ta, ops.tw, g, grid, s);
 }
 
 extern "C" int hds_restore_kv_proj(const void* latents, int64_t ld_latents, const void* w_kv, int64_t ldw, int T,

@@ -58,6 +58,10 @@ struct GemmArgs {
     int n_targets;            // number of valid accum pointers (1 for local / multicast)
     int red_mode;             // 0 = red.gpu  1 = red.sys to every accum[i]  2 = multimem.red on accum[0]
     int64_t ld_accum;
+    // split-K for EPI_STORE / EPI_GATED (single m-tile only): fp32 partial sums + one ticket per
+    // (n-tile, 32-row quadrant); the last split to arrive applies the epilogue and re-zeroes both
+    float* splitk_ws;         // [M, N] fp32, zero between calls
+    int32_t* splitk_tickets;  // [n_tiles * 4], zero between calls
     // EPI_KV_ROPE / EPI_QKV_ROPE
     void* kv_cache;           // this layer's cache: [blocks][2][n_kv_heads][block_size][head_dim]
     void* q_out;              // [M, n_q_heads * head_dim]
@@ -86,8 +90,66 @@ __device__ __forceinline__ void store_row32(void* dst, const float (&v)[32]) {
 // is the global token row owned by this thread (may be >= M: then only the collective tcgen05.ld
 // is executed and nothing is written).
 // ---------------------------------------------------------------------------------------------
-template <int BN, bool kBf16>
-__device__ __forceinline__ void epilogue_store(const GemmArgs& a, uint32_t taddr, int row, int n0) {
+// Apply the STORE epilogue to 32 consecutive accumulator columns [n, n+32) of one row.
+template <bool kBf16>
+__device__ __forceinline__ void store_chunk(const GemmArgs& a, int row, int n, float (&v)[32]) {
+    if (a.bias != nullptr) {
+#pragma unroll
+        for (int j = 0; j < 32; ++j)
+            if (n + j < a.N) v[j] += load_scalar<kBf16>(a.bias, n + j);
+    }
+    if (a.act != ACT_IDENTITY) {
+#pragma unroll
+        for (int j = 0; j < 32; ++j) v[j] = apply_act(v[j], a.act);
+    }
+    const int64_t off = static_cast<int64_t>(row) * a.ldo + n;
+    char* dst = reinterpret_cast<char*>(a.out) + off * 2;
+    if (n + 32 <= a.N && (reinterpret_cast<uintptr_t>(dst) & 15) == 0) {
+        store_row32<kBf16>(dst, v);
+    } else {
+        for (int j = 0; j < 32 && n + j < a.N; ++j) store_scalar<kBf16>(a.out, off + j, v[j]);
+    }
+}
+
+// GATED epilogue: N counts interleaved (gate, up) columns; the output has N/2 columns.
+template <bool kBf16>
+__device__ __forceinline__ void gated_chunk(const GemmArgs& a, int row, int n, float (&v)[32]) {
+    float o[16];
+#pragma unroll
+    for (int j = 0; j < 16; ++j) {
+        float g = v[2 * j];
+        float u = v[2 * j + 1];
+        if (a.bias != nullptr && n + 2 * j + 1 < a.N) {
+            g += load_scalar<kBf16>(a.bias, n + 2 * j);
+            u += load_scalar<kBf16>(a.bias, n + 2 * j + 1);
+        }
+        o[j] = apply_act(g, a.act) * u;
+    }
+    const int64_t off = static_cast<int64_t>(row) * a.ldo + (n >> 1);
+    char* dst = reinterpret_cast<char*>(a.out) + off * 2;
+    if (n + 32 <= a.N && (reinterpret_cast<uintptr_t>(dst) & 15) == 0) {
+        uint4* p = reinterpret_cast<uint4*>(dst);
+#pragma unroll
+        for (int i = 0; i < 2; ++i) {
+            uint4 q;
+            q.x = pack2<kBf16>(o[8 * i + 0], o[8 * i + 1]);
+            q.y = pack2<kBf16>(o[8 * i + 2], o[8 * i + 3]);
+            q.z = pack2<kBf16>(o[8 * i + 4], o[8 * i + 5]);
+            q.w = pack2<kBf16>(o[8 * i + 6], o[8 * i + 7]);
+            st_v4(p + i, q);
+        }
+    } else {
+        for (int j = 0; j < 16 && n + 2 * j + 1 < a.N; ++j) store_scalar<kBf16>(a.out, off + j, o[j]);
+    }
+}
+
+// STORE / GATED epilogue of one tile. With split-K (a.splits > 1, single m-tile) every split adds its
+// partial into the fp32 workspace; each warp takes a ticket for its 32-row quadrant and the last one
+// reads the finished sums back (L2), applies the epilogue and leaves workspace + ticket zeroed.
+template <int BN, bool kBf16, bool kGated>
+__device__ __forceinline__ void epilogue_store(const GemmArgs& a, uint32_t taddr, int row, int n0, int n_t,
+                                               uint32_t quad, uint32_t lane) {
+    const bool split = a.splits > 1;
 #pragma unroll 1
     for (int c = 0; c < BN; c += 32) {
         uint32_t r[32];
@@ -98,65 +160,56 @@ __device__ __forceinline__ void epilogue_store(const GemmArgs& a, uint32_t taddr
             float v[32];
 #pragma unroll
             for (int j = 0; j < 32; ++j) v[j] = __uint_as_float(r[j]);
-            if (a.bias != nullptr) {
-#pragma unroll
-                for (int j = 0; j < 32; ++j)
-                    if (n + j < a.N) v[j] += load_scalar<kBf16>(a.bias, n + j);
-            }
-            if (a.act != ACT_IDENTITY) {
-#pragma unroll
-                for (int j = 0; j < 32; ++j) v[j] = apply_act(v[j], a.act);
-            }
-            const int64_t off = static_cast<int64_t>(row) * a.ldo + n;
-            char* dst = reinterpret_cast<char*>(a.out) + off * 2;
-            if (n + 32 <= a.N && (reinterpret_cast<uintptr_t>(dst) & 15) == 0) {
-                store_row32<kBf16>(dst, v);
+            if (!split) {
+                if (kGated) gated_chunk<kBf16>(a, row, n, v);
+                else store_chunk<kBf16>(a, row, n, v);
             } else {
-                for (int j = 0; j < 32 && n + j < a.N; ++j) store_scalar<kBf16>(a.out, off + j, v[j]);
+                float* dst = a.splitk_ws + static_cast<int64_t>(row) * a.N + n;
+                if (n + 32 <= a.N && (a.N & 3) == 0) {
+#pragma unroll
+                    for (int j = 0; j < 32; j += 4) red_add_v4_f32(dst + j, v[j], v[j + 1], v[j + 2], v[j + 3]);
+                } else {
+                    for (int j = 0; j < 32 && n + j < a.N; ++j) atomicAdd(dst + j, v[j]);
+                }
             }
         }
     }
-}
-
-template <int BN, bool kBf16>
-__device__ __forceinline__ void epilogue_gated(const GemmArgs& a, uint32_t taddr, int row, int n0) {
-    // N counts interleaved (gate, up) columns; the output has N/2 columns.
+    if (!split) return;
+    if (static_cast<int>(quad * 32) >= a.M) return;  // no valid row in this quadrant (warp-uniform)
+    __threadfence();
+    __syncwarp();
+    int last = 0;
+    if (lane == 0) last = (atomicAdd(&a.splitk_tickets[n_t * 4 + quad], 1) == a.splits - 1) ? 1 : 0;
+    last = __shfl_sync(0xffffffffu, last, 0);
+    if (!last) return;
+    __threadfence();
+    if (row < a.M) {
 #pragma unroll 1
-    for (int c = 0; c < BN; c += 32) {
-        uint32_t r[32];
-        tmem_ld_32x32(taddr + c, r);
-        tmem_ld_wait();
-        const int n = n0 + c;
-        if (row < a.M && n < a.N) {
-            float o[16];
+        for (int c = 0; c < BN; c += 32) {
+            const int n = n0 + c;
+            if (n >= a.N) break;
+            float* src = a.splitk_ws + static_cast<int64_t>(row) * a.N + n;
+            float v[32];
+            if (n + 32 <= a.N && (a.N & 3) == 0) {
 #pragma unroll
-            for (int j = 0; j < 16; ++j) {
-                float g = __uint_as_float(r[2 * j]);
-                float u = __uint_as_float(r[2 * j + 1]);
-                if (a.bias != nullptr && n + 2 * j + 1 < a.N) {
-                    g += load_scalar<kBf16>(a.bias, n + 2 * j);
-                    u += load_scalar<kBf16>(a.bias, n + 2 * j + 1);
-                }
-                o[j] = apply_act(g, a.act) * u;
-            }
-            const int64_t off = static_cast<int64_t>(row) * a.ldo + (n >> 1);
-            char* dst = reinterpret_cast<char*>(a.out) + off * 2;
-            if (n + 32 <= a.N && (reinterpret_cast<uintptr_t>(dst) & 15) == 0) {
-                uint4* p = reinterpret_cast<uint4*>(dst);
-#pragma unroll
-                for (int i = 0; i < 2; ++i) {
-                    uint4 q;
-                    q.x = pack2<kBf16>(o[8 * i + 0], o[8 * i + 1]);
-                    q.y = pack2<kBf16>(o[8 * i + 2], o[8 * i + 3]);
-                    q.z = pack2<kBf16>(o[8 * i + 4], o[8 * i + 5]);
-                    q.w = pack2<kBf16>(o[8 * i + 6], o[8 * i + 7]);
-                    st_v4(p + i, q);
+                for (int j = 0; j < 32; j += 4) {
+                    const float4 t = __ldcg(reinterpret_cast<const float4*>(src + j));
+                    v[j] = t.x; v[j + 1] = t.y; v[j + 2] = t.z; v[j + 3] = t.w;
+                    __stcg(reinterpret_cast<float4*>(src + j), make_float4(0.f, 0.f, 0.f, 0.f));
                 }
             } else {
-                for (int j = 0; j < 16 && n + 2 * j + 1 < a.N; ++j) store_scalar<kBf16>(a.out, off + j, o[j]);
+#pragma unroll
+                for (int j = 0; j < 32; ++j) {
+                    v[j] = (n + j < a.N) ? __ldcg(src + j) : 0.0f;
+                    if (n + j < a.N) __stcg(src + j, 0.0f);
+                }
             }
+            if (kGated) gated_chunk<kBf16>(a, row, n, v);
+            else store_chunk<kBf16>(a, row, n, v);
         }
     }
+    __syncwarp();
+    if (lane == 0) a.splitk_tickets[n_t * 4 + quad] = 0;
 }
 
 template <int BN, bool kBf16>
@@ -214,68 +267,73 @@ __device__ __forceinline__ void epilogue_red(const GemmArgs& a, uint32_t taddr, 
     }
 }
 
-// One tile == one attention head (BN == head_dim). Rotate-half RoPE pairs column i with i + BN/2,
-// both of which live in this thread's accumulator row.
-template <int BN, bool kBf16, bool kHasQ>
+// A tile holds BN / HD whole attention heads. Rotate-half RoPE pairs column i with i + HD/2 of the
+// same head, both of which live in this thread's accumulator row.
+template <int BN, int HD, bool kBf16, bool kHasQ>
 __device__ __forceinline__ void epilogue_kv_rope(const GemmArgs& a, uint32_t taddr, int row, int n_tile) {
-    constexpr int HALF = BN / 2;
-    static_assert(HALF % 32 == 0, "head_dim must be 64 or 128 for the fused RoPE epilogue");
+    constexpr int HALF = HD / 2;
+    constexpr int HEADS = BN / HD;
+    static_assert(HALF % 32 == 0 && BN % HD == 0, "head_dim must be 64 or 128 and divide the tile width");
     const int n_q = kHasQ ? a.n_q_heads : 0;
-    const bool is_q = n_tile < n_q;
-    const int kv_idx = n_tile - n_q;                       // [0, 2*n_kv_heads)
-    const bool is_k = !is_q && kv_idx < a.n_kv_heads;
-    const int head = is_q ? n_tile : (is_k ? kv_idx : kv_idx - a.n_kv_heads);
-    const bool rope = a.do_rope && (is_q || is_k);
-
+    const int total_heads = n_q + 2 * a.n_kv_heads;
     int pos = 0, slot = -1;
     if (row < a.M) {
         pos = a.tok_pos[row];
         slot = a.tok_slot[row];
     }
-    char* dst = nullptr;
-    if (row < a.M) {
-        if (is_q) {
-            dst = reinterpret_cast<char*>(a.q_out) +
-                  (static_cast<int64_t>(row) * a.n_q_heads + head) * BN * 2;
-        } else if (slot >= 0) {
-            const int64_t blk = slot / a.block_size, off = slot % a.block_size;
-            const int64_t e = (((blk * 2 + (is_k ? 0 : 1)) * a.n_kv_heads + head) * a.block_size + off) * BN;
-            dst = reinterpret_cast<char*>(a.kv_cache) + e * 2;
-        }
-    }
-    const int col0 = n_tile * BN;
 #pragma unroll 1
-    for (int c = 0; c < HALF; c += 32) {
-        uint32_t rl[32], rh[32];
-        tmem_ld_32x32(taddr + c, rl);
-        tmem_ld_32x32(taddr + c + HALF, rh);
-        tmem_ld_wait();
-        if (dst != nullptr) {
-            float lo[32], hi[32];
-#pragma unroll
-            for (int j = 0; j < 32; ++j) {
-                lo[j] = __uint_as_float(rl[j]);
-                hi[j] = __uint_as_float(rh[j]);
+    for (int hh = 0; hh < HEADS; ++hh) {
+        const int gh = n_tile * HEADS + hh;  // global head index over [Q heads | K heads | V heads]
+        if (gh >= total_heads) break;         // warp-uniform
+        const bool is_q = gh < n_q;
+        const int kv_idx = gh - n_q;
+        const bool is_k = !is_q && kv_idx < a.n_kv_heads;
+        const int head = is_q ? gh : (is_k ? kv_idx : kv_idx - a.n_kv_heads);
+        const bool rope = a.do_rope && (is_q || is_k);
+        char* dst = nullptr;
+        if (row < a.M) {
+            if (is_q) {
+                dst = reinterpret_cast<char*>(a.q_out) + (static_cast<int64_t>(row) * a.n_q_heads + head) * HD * 2;
+            } else if (slot >= 0) {
+                const int64_t blk = slot / a.block_size, off = slot % a.block_size;
+                const int64_t e = (((blk * 2 + (is_k ? 0 : 1)) * a.n_kv_heads + head) * a.block_size + off) * HD;
+                dst = reinterpret_cast<char*>(a.kv_cache) + e * 2;
             }
-            if (a.bias != nullptr) {
+        }
+        const int col0 = gh * HD;
+#pragma unroll 1
+        for (int c = 0; c < HALF; c += 32) {
+            uint32_t rl[32], rh[32];
+            tmem_ld_32x32(taddr + hh * HD + c, rl);
+            tmem_ld_32x32(taddr + hh * HD + c + HALF, rh);
+            tmem_ld_wait();
+            if (dst != nullptr) {
+                float lo[32], hi[32];
 #pragma unroll
                 for (int j = 0; j < 32; ++j) {
-                    lo[j] += load_scalar<kBf16>(a.bias, col0 + c + j);
-                    hi[j] += load_scalar<kBf16>(a.bias, col0 + c + HALF + j);
+                    lo[j] = __uint_as_float(rl[j]);
+                    hi[j] = __uint_as_float(rh[j]);
                 }
-            }
-            if (rope) {
+                if (a.bias != nullptr) {
+#pragma unroll
+                    for (int j = 0; j < 32; ++j) {
+                        lo[j] += load_scalar<kBf16>(a.bias, col0 + c + j);
+                        hi[j] += load_scalar<kBf16>(a.bias, col0 + c + HALF + j);
+                    }
+                }
+                if (rope) {
 #pragma unroll 4
-                for (int j = 0; j < 32; ++j) {
-                    float s, co;
-                    sincosf(static_cast<float>(pos) * a.inv_freq[c + j], &s, &co);
-                    const float x = lo[j], y = hi[j];
-                    lo[j] = x * co - y * s;
-                    hi[j] = y * co + x * s;
+                    for (int j = 0; j < 32; ++j) {
+                        float sn, co;
+                        sincosf(static_cast<float>(pos) * a.inv_freq[c + j], &sn, &co);
+                        const float x = lo[j], y = hi[j];
+                        lo[j] = x * co - y * sn;
+                        hi[j] = y * co + x * sn;
+                    }
                 }
+                store_row32<kBf16>(dst + c * 2, lo);
+                store_row32<kBf16>(dst + (c + HALF) * 2, hi);
             }
-            store_row32<kBf16>(dst + c * 2, lo);
-            store_row32<kBf16>(dst + (c + HALF) * 2, hi);
         }
     }
 }
@@ -283,7 +341,7 @@ __device__ __forceinline__ void epilogue_kv_rope(const GemmArgs& a, uint32_t tad
 // ---------------------------------------------------------------------------------------------
 // The kernel
 // ---------------------------------------------------------------------------------------------
-template <int BN, int EPI, bool kBf16>
+template <int BN, int EPI, bool kBf16, int HD = 128>
 __global__ void __launch_bounds__(kGemmThreads, 1)
 gemm_tn_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_w,
                const GemmArgs args) {
@@ -408,15 +466,15 @@ gemm_tn_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
             const uint32_t taddr = tmem_base + ((quad * 32u) << 16) + acc * BN;
             const int row = m_t * kGemmBM + quad * 32 + lane;
             if constexpr (EPI == EPI_STORE)
-                epilogue_store<BN, kBf16>(args, taddr, row, n_t * BN);
+                epilogue_store<BN, kBf16, false>(args, taddr, row, n_t * BN, n_t, quad, lane);
             else if constexpr (EPI == EPI_GATED)
-                epilogue_gated<BN, kBf16>(args, taddr, row, n_t * BN);
+                epilogue_store<BN, kBf16, true>(args, taddr, row, n_t * BN, n_t, quad, lane);
             else if constexpr (EPI == EPI_RED_F32)
                 epilogue_red<BN, kBf16>(args, taddr, row, n_t * BN, sp == 0);
             else if constexpr (EPI == EPI_KV_ROPE)
-                epilogue_kv_rope<BN, kBf16, false>(args, taddr, row, n_t);
+                epilogue_kv_rope<BN, HD, kBf16, false>(args, taddr, row, n_t);
             else
-                epilogue_kv_rope<BN, kBf16, true>(args, taddr, row, n_t);
+                epilogue_kv_rope<BN, HD, kBf16, true>(args, taddr, row, n_t);
             tc_fence_before();
             __syncwarp();
             if (lane == 0) mbar_arrive(&tempty_bar[acc]);

@@ -64,18 +64,20 @@ __device__ __forceinline__ bool mbar_try_wait(uint64_t* bar, uint32_t parity) {
         : "memory");
     return ok != 0;
 }
-__device__ __forceinline__ uint64_t global_timer_ns() {
-    uint64_t t;
-    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
-    return t;
-}
 // Bounded wait: a protocol bug traps (-> CUDA error on the host) instead of hanging the GPU.
-// Legitimate waits in these kernels are microseconds to a few milliseconds; 4 s means deadlock.
+// The bound uses the SM-local cycle counter, read only once per 4096 failed probes (reading
+// %globaltimer per probe costs about a microsecond and showed up as per-tile latency).
+// Legitimate waits here are microseconds to milliseconds; ~2^33 cycles (> 4 s) means deadlock.
 __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
     if (mbar_try_wait(bar, parity)) return;
-    const uint64_t t0 = global_timer_ns();
+    uint32_t probes = 0;
+    long long t0 = 0;
     while (!mbar_try_wait(bar, parity)) {
-        if (global_timer_ns() - t0 > 4000000000ull) __trap();
+        if ((++probes & 4095u) == 0) {
+            const long long now = clock64();
+            if (t0 == 0) t0 = now;
+            else if (now - t0 > (1ll << 33)) __trap();
+        }
     }
 }
 

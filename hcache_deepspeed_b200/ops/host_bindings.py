@@ -1,0 +1,49 @@
+"""ctypes declarations for ``libhds_host.so`` (``include/hds_host.h``)."""
+from __future__ import annotations
+
+import ctypes
+from ctypes import POINTER, Structure, c_char_p, c_int, c_int32, c_int64, c_void_p
+
+
+class SeqIn(Structure):
+    """Mirror of ``hds_seq_in``."""
+    _fields_ = [("n_new", c_int32), ("seen", c_int32), ("n_blocks", c_int32), ("_pad", c_int32),
+                ("block_ids", c_void_p)]
+
+
+def declare(lib: ctypes.CDLL) -> None:
+    P, I, I32, L = c_void_p, c_int, c_int32, c_int64
+    lib.hds_alloc_create.argtypes = [I32]
+    lib.hds_alloc_create.restype = P
+    lib.hds_alloc_destroy.argtypes = [P]
+    lib.hds_alloc_destroy.restype = None
+    lib.hds_alloc_allocate.argtypes = [P, I32, P]
+    lib.hds_alloc_allocate.restype = I
+    lib.hds_alloc_free.argtypes = [P, P, I32]
+    lib.hds_alloc_free.restype = I
+    lib.hds_alloc_free_blocks.argtypes = [P]
+    lib.hds_alloc_free_blocks.restype = I32
+    lib.hds_alloc_total_blocks.argtypes = [P]
+    lib.hds_alloc_total_blocks.restype = I32
+
+    lib.hds_build_batch.argtypes = [POINTER(SeqIn), I32, I32, I32, I32, I32, I32, I32, I32, P, P, P, P, P, P, P, P]
+    lib.hds_build_batch.restype = I
+
+    lib.hds_aio_create.argtypes = [L, I32, I32, I32]
+    lib.hds_aio_create.restype = P
+    lib.hds_aio_destroy.argtypes = [P]
+    lib.hds_aio_destroy.restype = None
+    lib.hds_aio_pread.argtypes = [P, P, c_char_p, L, L]
+    lib.hds_aio_pread.restype = L
+    lib.hds_aio_pwrite.argtypes = [P, P, c_char_p, L, L]
+    lib.hds_aio_pwrite.restype = L
+    lib.hds_aio_wait.argtypes = [P, L]
+    lib.hds_aio_wait.restype = L
+    lib.hds_aio_poll.argtypes = [P, L]
+    lib.hds_aio_poll.restype = I
+    lib.hds_aio_pending.argtypes = [P]
+    lib.hds_aio_pending.restype = I32
+    lib.hds_mem_lock.argtypes = [P, L]
+    lib.hds_mem_lock.restype = I
+    lib.hds_mem_unlock.argtypes = [P, L]
+    lib.hds_mem_unlock.restype = I

@@ -54,9 +54,15 @@ def _check_2d(t: torch.Tensor, name: str) -> None:
         raise ValueError(f"{name} must be 2-D with a contiguous last dimension, got {tuple(t.shape)} / {t.stride()}")
 
 
+def gemm_splitk_workspace_bytes(M: int, N: int) -> int:
+    return int(native.cuda_lib().hds_gemm_splitk_workspace_bytes(M, N))
+
+
 def gemm(a: torch.Tensor, w: torch.Tensor, bias: Optional[torch.Tensor] = None, act: int = ACT_IDENTITY,
-         gated: bool = False, out: Optional[torch.Tensor] = None, bn: int = 0) -> torch.Tensor:
-    """``out = epilogue(a @ w.T + bias)`` on the tcgen05 GEMM. ``gated``: interleaved (gate, up) columns."""
+         gated: bool = False, out: Optional[torch.Tensor] = None, bn: int = 0, splits: int = 0,
+         workspace: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """``out = epilogue(a @ w.T + bias)`` on the tcgen05 GEMM. ``gated``: interleaved (gate, up) columns.
+    ``workspace`` (zero-initialised uint8 scratch) enables split-K for decode-size M."""
     _check_2d(a, "a")
     _check_2d(w, "w")
     M, K = a.shape
@@ -68,7 +74,8 @@ def gemm(a: torch.Tensor, w: torch.Tensor, bias: Optional[torch.Tensor] = None, 
     _check_2d(out, "out")
     lib = native.cuda_lib()
     rc = lib.hds_gemm(_p(a), a.stride(0), _p(w), w.stride(0), M, N, K, _dt(a), EPI_GATED if gated else EPI_STORE,
-                      act, _p(bias), _p(out), out.stride(0), bn, _stream())
+                      act, _p(bias), _p(out), out.stride(0), bn, splits, _p(workspace),
+                      0 if workspace is None else workspace.numel() * workspace.element_size(), _stream())
     native.check(rc, "hds_gemm")
     _count()
     return out
@@ -230,12 +237,19 @@ def paged_attention_splitkv(q: torch.Tensor, out: torch.Tensor, kv_cache_layer: 
     _count()
 
 
+def prefill_workspace_bytes(n_items: int, n_q_heads: int, head_dim: int, n_splits: int) -> int:
+    return int(native.cuda_lib().hds_paged_attention_prefill_workspace_bytes(n_items, n_q_heads, head_dim, n_splits))
+
+
 def paged_attention_prefill(q: torch.Tensor, out: torch.Tensor, kv_cache_layer: torch.Tensor,
                             block_tables: torch.Tensor, items: torch.Tensor, n_items: int, n_q_heads: int,
-                            n_kv_heads: int, head_dim: int, block_size: int, scale: float) -> None:
+                            n_kv_heads: int, head_dim: int, block_size: int, scale: float, n_splits: int = 1,
+                            workspace: Optional[torch.Tensor] = None) -> None:
     lib = native.cuda_lib()
     rc = lib.hds_paged_attention_prefill(_p(q), _p(out), _p(kv_cache_layer), kv_cache_layer.shape[0], _p(block_tables),
                                          block_tables.stride(0), _p(items), n_items, q.shape[0], n_q_heads, n_kv_heads,
-                                         head_dim, block_size, scale, _dt(q), _stream())
+                                         head_dim, block_size, scale, n_splits, _p(workspace),
+                                         0 if workspace is None else workspace.numel() * workspace.element_size(),
+                                         _dt(q), _stream())
     native.check(rc, "hds_paged_attention_prefill")
     _count()

@@ -35,7 +35,7 @@ def _declare_cuda(lib: ctypes.CDLL) -> None:
     lib.hds_last_error.restype = c_char_p
     lib.hds_last_error.argtypes = []
     sigs = {
-        "hds_gemm": [P, L, P, L, I, I, I, I, I, I, P, P, L, I, P],
+        "hds_gemm": [P, L, P, L, I, I, I, I, I, I, P, P, L, I, I, P, L, P],
         "hds_gemm_accum": [P, L, P, L, I, I, I, I, P, P, I, I, L, I, I, P],
         "hds_restore_kv_proj": [P, L, P, L, I, I, I, P, P, P, P, P, I, I, I, I, P],
         "hds_qkv_rope_proj": [P, L, P, L, I, I, I, P, P, P, P, P, P, I, I, I, I, I, P],
@@ -47,7 +47,7 @@ def _declare_cuda(lib: ctypes.CDLL) -> None:
         "hds_kv_blocks_copy": [P, P, P, I, I, L, L, I, P],
         "hds_cvt_f32": [P, P, L, I, I, P],
         "hds_paged_attention_splitkv": [P, P, P, L, P, I, P, I, I, I, I, I, I, I, F, P, L, I, P],
-        "hds_paged_attention_prefill": [P, P, P, L, P, I, P, I, I, I, I, I, I, F, I, P],
+        "hds_paged_attention_prefill": [P, P, P, L, P, I, P, I, I, I, I, I, I, F, I, P, L, I, P],
     }
     for name, argtypes in sigs.items():
         fn = getattr(lib, name)
@@ -55,6 +55,10 @@ def _declare_cuda(lib: ctypes.CDLL) -> None:
         fn.restype = c_int
     lib.hds_paged_attention_splitkv_workspace_bytes.argtypes = [I, I, I, I, I, I]
     lib.hds_paged_attention_splitkv_workspace_bytes.restype = c_int64
+    lib.hds_paged_attention_prefill_workspace_bytes.argtypes = [I, I, I, I]
+    lib.hds_paged_attention_prefill_workspace_bytes.restype = c_int64
+    lib.hds_gemm_splitk_workspace_bytes.argtypes = [I, I]
+    lib.hds_gemm_splitk_workspace_bytes.restype = c_int64
     # optional entry points (declared when present so older builds keep loading)
     optional = {
         "hds_tp_barrier": ([P, I, I, P], c_int),

@@ -29,9 +29,14 @@ const char* hds_last_error(void);
 /* out = epilogue(A[M,K] * W[N,K]^T + bias).  epilogue 0: act();  1: gated — columns are interleaved
  * (gate, up) pairs, out has N/2 columns: out[:, j] = act(c[2j]) * c[2j+1].  act: 0 id, 1 gelu, 2 relu,
  * 3 silu, 4 gelu-tanh.  bn: tile width override (0 = heuristic).
- * Ref: core_ops/blas_kernels/blas.h:31-136 + bias_activations + gated_activations. */
+ * Ref: core_ops/blas_kernels/blas.h:31-136 + bias_activations + gated_activations.
+ * Split-K (decode-size M <= 128): pass a zero-initialised scratch buffer of at least
+ * hds_gemm_splitk_workspace_bytes(M, N) bytes; partial sums meet there and the last split applies the
+ * epilogue and leaves the buffer zeroed again. splits: 0 = heuristic, 1 = off. Without scratch: no split. */
+int64_t hds_gemm_splitk_workspace_bytes(int M, int N);
 int hds_gemm(const void* A, int64_t lda, const void* W, int64_t ldw, int M, int N, int K, int dtype, int epilogue,
-             int act, const void* bias, void* out, int64_t ldo, int bn, void* stream);
+             int act, const void* bias, void* out, int64_t ldo, int bn, int splits, void* splitk_ws,
+             int64_t splitk_ws_bytes, void* stream);
 
 /* accum[M,N] (fp32) += A * W^T (+ bias once).  Split-K partial sums and tensor-parallel partial sums share
  * this path: red_mode 0 = local red.add; 1 = red.add (system scope) into each of n_targets peer mappings of
@@ -130,12 +135,16 @@ int hds_paged_attention_splitkv(const void* q, void* out, const void* kv_cache_l
 
 /* tcgen05 paged attention for items with up to 128 query tokens (prefill / chunked continuation): QK^T and
  * PV on the tensor cores with TMEM accumulators, TMA page gathers, online softmax in registers.
- * n_q_rows = total rows of q (bounds the Q tensor map). The KV cache must hold finite values everywhere
+ * n_q_rows = total rows of q (bounds the Q tensor map). n_splits > 1 splits each item's KV range over several
+ * CTAs (short continuation over a long restored context); partials merge in `workspace` by ticket. The KV cache must hold finite values everywhere
  * (allocate it zeroed): masked probabilities are exact zeros, but 0 * NaN would still poison a row. */
 int hds_paged_attention_prefill(const void* q, void* out, const void* kv_cache_layer, int64_t num_blocks,
                                 const int32_t* block_tables, int max_blocks_per_seq, const hds_attn_item* items,
                                 int n_items, int n_q_rows, int n_q_heads, int n_kv_heads, int head_dim, int block_size,
-                                float scale, int dtype, void* stream);
+                                float scale, int n_splits, void* workspace, int64_t workspace_bytes, int dtype,
+                                void* stream);
+/* Scratch bytes for n_splits > 1 (0 when n_splits <= 1). Zero it once; the kernel leaves its tickets zeroed. */
+int64_t hds_paged_attention_prefill_workspace_bytes(int n_items, int n_q_heads, int head_dim, int n_splits);
 
 #ifdef __cplusplus
 }

@@ -1,0 +1,78 @@
+/* hds_host.h — C ABI of libhds_host.so, the host-side native runtime of hcache_deepspeed_b200.
+ * No CUDA dependency: it builds and is tested on CPU-only machines.
+ *
+ *   - KV block allocator            (ref: deepspeed/inference/v2/ragged/blocked_allocator.py:11-105 — a Python
+ *                                    linked list with one .item() per block)
+ *   - ragged batch builder          (ref: ragged/ragged_wrapper.py:134-218 insert_sequence/finalize python lists,
+ *                                    kernels/ragged_ops/atom_builder/atom_builder.cpp:10-53)
+ *   - asynchronous file I/O handle  (ref: csrc/aio/py_lib/deepspeed_py_io_handle.cpp, py_ds_aio.cpp:15-116 —
+ *                                    libaio; here a thread pool over pread/pwrite with optional O_DIRECT,
+ *                                    because libaio headers are not part of the target image)
+ */
+#ifndef HDS_HOST_H
+#define HDS_HOST_H
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+/* ---- KV block allocator: O(1) allocate/free of block ids, double-free detection ---------------- */
+void* hds_alloc_create(int32_t num_blocks);
+void hds_alloc_destroy(void* h);
+/* Writes n block ids to out. Returns 0, or -1 (nothing allocated) when fewer than n blocks are free. */
+int hds_alloc_allocate(void* h, int32_t n, int32_t* out);
+/* Returns 0, or -1 if any id is out of range or already free (nothing is freed in that case). */
+int hds_alloc_free(void* h, const int32_t* ids, int32_t n);
+int32_t hds_alloc_free_blocks(void* h);
+int32_t hds_alloc_total_blocks(void* h);
+
+/* ---- ragged batch builder ------------------------------------------------------------------------ */
+/* One sequence of the batch as the builder sees it. */
+typedef struct {
+    int32_t n_new;            /* tokens in flight this forward */
+    int32_t seen;             /* tokens already in the KV cache */
+    int32_t n_blocks;         /* valid entries of block_ids */
+    int32_t _pad;
+    const int32_t* block_ids; /* this sequence's KV block ids, in order */
+} hds_seq_in;
+
+/* Output arrays (all int32, caller-allocated, typically views of ONE pinned staging buffer):
+ *   tok_pos[T], tok_slot[T], tok_seq[T]     per token: absolute position, cache slot, batch-local sequence
+ *   last_rows[n_seqs]                        row of each sequence's last in-flight token
+ *   block_tables[n_seqs * table_stride]      block ids, zero padded
+ *   items_small / items_large [.. * 4]       attention work items (seq, q_row0, n_q, pos0), see hds_attn_item
+ * rows_small_max: max query rows (tokens * q-heads-per-kv-head) a split-KV item may carry (<= 8);
+ * group: q heads per kv head; large_chunk: max tokens per tensor-core item (128).
+ * counts[0] = total tokens, [1] = n small items, [2] = n large items, [3] = max rows per small item,
+ * [4] = max kv length over small items, [5] = max kv length over large items.
+ * Returns 0, -1 on capacity overflow (max_tokens / max_items / table_stride), -2 if a sequence lacks blocks. */
+int hds_build_batch(const hds_seq_in* seqs, int32_t n_seqs, int32_t block_size, int32_t group, int32_t rows_small_max,
+                    int32_t large_chunk, int32_t max_tokens, int32_t max_items, int32_t table_stride,
+                    int32_t* tok_pos, int32_t* tok_slot, int32_t* tok_seq, int32_t* last_rows, int32_t* block_tables,
+                    int32_t* items_small, int32_t* items_large, int32_t* counts);
+
+/* ---- asynchronous file I/O ----------------------------------------------------------------------- */
+/* Thread-pool handle: requests are split into block_size pieces spread over `threads` workers, each piece
+ * a pread/pwrite at its own offset (O_DIRECT when use_direct and buffer/offset/length are 4096-aligned).
+ * Ref semantics: aio_handle(block_size, queue_depth, single_submit, overlap_events, intra_op_parallelism). */
+void* hds_aio_create(int64_t block_size, int32_t queue_depth, int32_t threads, int32_t use_direct);
+void hds_aio_destroy(void* h);
+/* Asynchronous: returns a request id > 0 (or -1 when the file cannot be opened). */
+int64_t hds_aio_pread(void* h, void* buffer, const char* path, int64_t nbytes, int64_t file_offset);
+int64_t hds_aio_pwrite(void* h, const void* buffer, const char* path, int64_t nbytes, int64_t file_offset);
+/* Block until the request (or every outstanding request if id == 0) has finished.
+ * Returns bytes transferred by that request (sum for id == 0) or -errno of the first failure. */
+int64_t hds_aio_wait(void* h, int64_t request_id);
+/* 1 if finished, 0 if still running, negative on unknown id. Never blocks. */
+int hds_aio_poll(void* h, int64_t request_id);
+int32_t hds_aio_pending(void* h);
+
+/* mlock / munlock helpers for page-locked staging buffers that are not CUDA-registered. */
+int hds_mem_lock(void* ptr, int64_t nbytes);
+int hds_mem_unlock(void* ptr, int64_t nbytes);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* HDS_HOST_H */

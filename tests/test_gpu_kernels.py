@@ -44,6 +44,20 @@ def test_gemm_store(dtype, M, N, K_, bn):
     torch.testing.assert_close(out.float(), want, **tol(dtype))
 
 
+@pytest.mark.parametrize("M,N,K_,bn,splits,gated", [(16, 4096, 4096, 128, 4, False), (1, 12288, 4096, 0, 0, False),
+                                                    (64, 2 * 1376, 2048, 64, 3, True), (100, 520, 1024, 128, 2, False),
+                                                    (8, 22016, 4096, 0, 0, True)])
+def test_gemm_store_splitk(M, N, K_, bn, splits, gated):
+    torch.manual_seed(12)
+    a, w, b = rand(M, K_), rand(N, K_, scale=K_ ** -0.5), rand(N)
+    ws = torch.zeros(K().gemm_splitk_workspace_bytes(M, N), dtype=torch.uint8, device="cuda")
+    want = ref.gemm(a, w, bias=b, act=3 if gated else 0, gated=gated, out_dtype=torch.float32)
+    for _ in range(2):  # second call: scratch must have been left zeroed
+        out = K().gemm(a, w, bias=b, act=3 if gated else 0, gated=gated, bn=bn, splits=splits, workspace=ws)
+        torch.testing.assert_close(out.float(), want, **tol(torch.bfloat16))
+    assert int(ws.view(torch.int32).abs().max()) == 0
+
+
 @pytest.mark.parametrize("act", [1, 2, 3, 4])
 def test_gemm_bias_act(act):
     torch.manual_seed(1)
@@ -316,3 +330,11 @@ def test_attention_prefill(dtype, n_q_heads, n_kv, d, bs):
     K().paged_attention_prefill(q, out, cache, tables, items_t, len(items), n_q_heads, n_kv, d, bs, scale)
     want = ref.paged_attention(q, cache, tables, items_t.cpu(), n_q_heads, n_kv, scale)
     torch.testing.assert_close(out.float(), want.float(), **tol(dtype))
+    # split-KV variant (partials merged through scratch); twice to check the tickets were reset
+    for n_splits in (3, 8):
+        ws = torch.zeros(K().prefill_workspace_bytes(len(items), n_q_heads, d, n_splits), dtype=torch.uint8, device="cuda")
+        for _ in range(2):
+            out.zero_()
+            K().paged_attention_prefill(q, out, cache, tables, items_t, len(items), n_q_heads, n_kv, d, bs, scale,
+                                        n_splits=n_splits, workspace=ws)
+            torch.testing.assert_close(out.float(), want.float(), **tol(dtype))
