@@ -1,0 +1,268 @@
+"""The ragged inference engine.
+
+Public surface of the reference's ``InferenceEngineV2`` (``deepspeed/inference/v2/engine_v2.py:30-301``):
+``put`` (returns ``(logits, per-sequence latents)`` as in the HCache fork, lines 131-189), ``restore_kv``
+(lines 107-128), ``query``, ``can_schedule``, ``get_remaining_block_capacity``, ``flush``, ``serialize``,
+``free_blocks``, ``n_kv_cache_groups``, ``model``.
+
+Defects of the fork that are NOT reproduced:
+* ``put`` works for every model family, not only Llama-2 (the fork unpacks a 2-tuple that only the Llama
+  model returns);
+* ``restore_kv`` skips ``None`` latents without dereferencing missing sequences, and compares with ``is None``
+  rather than an elementwise tensor ``==``;
+* capture can be switched off (globally or per call) and does not force a blocking ``.cpu()`` per forward;
+* under tensor parallelism only rank 0 copies latents to the host (they are replicated across ranks).
+"""
+from __future__ import annotations
+
+import json
+import os
+import pickle
+from typing import Iterable, List, Optional, Sequence, Tuple, Union
+
+import torch
+
+from ...utils.logging import inference_logger
+from .config_v2 import RaggedInferenceEngineConfig
+from .ragged import DSStateManager, PlaceholderSequenceDescriptor, RaggedBatchWrapper
+from .scheduling_utils import SchedulingError, SchedulingResult
+
+INFERENCE_MODEL_TIMER = "model-forward-inference"
+
+
+class LatentHandle:
+    """Hidden states of one sequence whose device-to-host copy may still be in flight (capture='async')."""
+
+    def __init__(self, tensor: torch.Tensor, event) -> None:
+        self._tensor, self._event = tensor, event
+
+    def wait(self) -> torch.Tensor:
+        if self._event is not None:
+            self._event.synchronize()
+            self._event = None
+        return self._tensor
+
+    @property
+    def shape(self):
+        return self._tensor.shape
+
+    def ready(self) -> bool:
+        return self._event is None or self._event.query()
+
+
+class InferenceEngineV2:
+
+    def __init__(self, policy, engine_config: RaggedInferenceEngineConfig) -> None:
+        """``policy``: an :class:`InferenceV2Policy` (model description + checkpoint engine)."""
+        self._config = engine_config
+        self._policy = policy
+        self._base_mp_group = self._initialize_tp_group()
+        inference_logger().info("Building model...")
+        self._model = self._policy.build_model(self._config, self._base_mp_group)
+        inference_logger().info("Model built.")
+        kv_cfg = self._model.kv_cache_config()
+        group = max(1, self._model.n_q // max(1, self._model.n_kv))
+        self._batch = RaggedBatchWrapper(self._config.state_manager, block_size=kv_cfg[0].block_size,
+                                         max_blocks_per_seq=kv_cfg[0].max_blocks_per_allocation_group, group=group,
+                                         device=self._model.device)
+        self._state_manager = DSStateManager(self._config.state_manager, kv_cfg, base_mp_group=self._base_mp_group,
+                                             device=self._model.device)
+        self._model.set_state_manager(self._state_manager)
+        self._capture_stream = torch.cuda.Stream(device=self._model.device) if self._model.device.type == "cuda" else None
+        self.last_put_stats = {}
+
+    # ------------------------------------------------------------------------------------------------
+    def _initialize_tp_group(self):
+        tp = self._config.tensor_parallel.tp_size
+        local_rank = int(os.getenv("LOCAL_RANK", 0))
+        if torch.cuda.is_available():
+            torch.cuda.set_device(local_rank % max(1, torch.cuda.device_count()))
+        if tp == 1:
+            return None
+        from ...comm import comm as dist
+        dist.init_distributed()
+        if local_rank >= tp:
+            raise RuntimeError("Local rank is greater than TP size, ensure that the TP config is correct.")
+        return dist.new_group(ranks=list(range(tp)))
+
+    @property
+    def free_blocks(self) -> torch.Tensor:
+        """Free KV blocks per cache group (shape ``[n_kv_cache_groups]``)."""
+        return self._state_manager.free_blocks
+
+    @property
+    def n_kv_cache_groups(self) -> int:
+        return self._state_manager.n_kv_cache_groups
+
+    def model(self):
+        return self._model
+
+    @property
+    def state_manager(self) -> DSStateManager:
+        return self._state_manager
+
+    @property
+    def config(self) -> RaggedInferenceEngineConfig:
+        return self._config
+
+    # ------------------------------------------------------------------------------------------------
+    # HCache restore
+    # ------------------------------------------------------------------------------------------------
+    def restore_kv(self, batch_uids: Iterable[int], batch_tokens: Iterable[torch.Tensor],
+                   batch_latents: Iterable[Optional[Union[torch.Tensor, LatentHandle]]],
+                   layers: Optional[Sequence[int]] = None, do_checks: bool = True) -> None:
+        """Rebuild the KV cache of ``batch_uids`` from saved hidden states instead of recomputing the prompt.
+
+        ``batch_tokens`` only supply the token counts (ref: engine_v2.py:108-128); ``batch_latents[i]`` is the host
+        tensor ``[n_layers, n_tokens_i, hidden]`` returned by earlier ``put`` calls (concatenated along dim 1 by the
+        caller if it spans several calls), or None to skip that uid. After the call the sequences have
+        ``seen_tokens`` advanced; follow with a normal ``put`` of the new turn's tokens.
+        """
+        uids, toks, lats = list(batch_uids), list(batch_tokens), list(batch_latents)
+        todo = [(u, t, (l.wait() if isinstance(l, LatentHandle) else l)) for u, t, l in zip(uids, toks, lats)
+                if l is not None]
+        if not todo:
+            return
+        if do_checks:
+            check = self.can_schedule([u for u, _, _ in todo], [int(t.numel()) for _, t, _ in todo])
+            if check != SchedulingResult.Success:
+                raise SchedulingError(check)
+        for u, t, l in todo:
+            if l.dim() != 3 or int(l.shape[1]) != int(t.numel()):
+                raise ValueError(f"latents of uid {u} have shape {tuple(l.shape)}, expected [layers, {int(t.numel())}, hidden]")
+        self._batch.clear()
+        for uid, tokens, _ in todo:
+            seq = self._state_manager.get_or_create_sequence(uid)
+            self._model.maybe_allocate_kv(seq, tokens.numel())
+            seq.pre_forward(tokens.numel())
+            self._batch.insert_sequence(seq, tokens, do_checks=do_checks)
+        self._batch.finalize()
+        self._model.restore_kv(self._batch, [l for _, _, l in todo], layers=layers)
+        for uid, _, _ in todo:
+            self._state_manager.get_sequence(uid).post_forward()
+
+    # ------------------------------------------------------------------------------------------------
+    # forward
+    # ------------------------------------------------------------------------------------------------
+    def put(self, batch_uids: Iterable[int], batch_tokens: Iterable[torch.Tensor], do_checks: bool = True,
+            capture_latents: Optional[bool] = None) -> Tuple[torch.Tensor, List]:
+        """One forward over a ragged batch. Returns ``(logits [len(batch_uids), vocab], latents)`` where
+        ``latents[i]`` is sequence i's ``[n_layers, n_tokens_i, hidden]`` host tensor (pinned), a
+        :class:`LatentHandle` in async mode, or None when capture is off."""
+        uids, toks = list(batch_uids), list(batch_tokens)
+        if do_checks:
+            check = self.can_schedule(uids, [int(t.numel()) for t in toks])
+            if check != SchedulingResult.Success:
+                raise SchedulingError(check)
+        self._batch.clear()
+        for uid, tokens in zip(uids, toks):
+            seq = self._state_manager.get_or_create_sequence(uid)
+            self._model.maybe_allocate_kv(seq, tokens.numel())
+            seq.pre_forward(tokens.numel())
+            self._batch.insert_sequence(seq, tokens, do_checks=do_checks)
+        self._batch.finalize()
+        self._model.prepare_batch(self._batch)
+
+        hc = self._config.hcache
+        capture = capture_latents
+        if capture is None:
+            capture = hc.enabled and hc.capture != "off"
+            if capture and not hc.capture_decode_steps and self._batch.current_tokens == self._batch.current_sequences:
+                capture = False
+        logits, latent_dev = self._model.forward(self._batch, capture=bool(capture))
+        latents = self._export_latents(latent_dev) if capture else [None] * len(uids)
+        assert logits.shape[0] == self._batch.current_sequences
+        for uid in uids:
+            seq = self._state_manager.get_sequence(uid)
+            seq.post_forward()
+            self._model.maybe_free_kv(seq)
+        return logits, latents
+
+    def _export_latents(self, latent_dev: torch.Tensor) -> List:
+        """Device ``[L, T, H]`` -> one pinned host tensor, split into per-sequence views (engine_v2.py:172-179)."""
+        shadow = self._batch.inflight_seq_descriptors_shadow
+        mode = self._config.hcache.capture
+        if self._model.tp_size > 1 and self._model.tp_rank != 0:
+            return [None] * len(shadow)  # replicated across ranks: one host copy is enough
+        if latent_dev.device.type != "cuda":
+            host = latent_dev.clone()
+            return [host[:, b:b + n] for b, n, _ in shadow]
+        host = torch.empty(latent_dev.shape, dtype=latent_dev.dtype, pin_memory=True)
+        comp = torch.cuda.current_stream()
+        cs = self._capture_stream
+        cs.wait_stream(comp)
+        with torch.cuda.stream(cs):
+            host.copy_(latent_dev, non_blocking=True)
+            ev = torch.cuda.Event()
+            ev.record(cs)
+        # the model's latent buffer is reused by the next forward: make that forward wait for this copy
+        comp.wait_event(ev)
+        views = [host[:, b:b + n] for b, n, _ in shadow]
+        if mode == "async":
+            return [LatentHandle(v, ev) for v in views]
+        ev.synchronize()
+        return views
+
+    # ------------------------------------------------------------------------------------------------
+    # scheduling helpers
+    # ------------------------------------------------------------------------------------------------
+    def query(self, uid: int, max_request_tokens: int, max_request_blocks) -> Tuple[int, int]:
+        """Tokens and KV blocks that scheduling up to ``max_request_tokens`` for ``uid`` would take."""
+        seq = self._state_manager.get_sequence(uid)
+        if seq is None:
+            if self._state_manager.n_tracked_sequences == self._config.state_manager.max_tracked_sequences:
+                return (0, 0)
+            seq = PlaceholderSequenceDescriptor()
+        return self._model.get_kv_requirements(seq, max_request_tokens, max_request_blocks)
+
+    def can_schedule(self, uids: Iterable[int], lengths: Iterable[int]) -> SchedulingResult:
+        """Dry-run a batch (ref: engine_v2.py:217-264)."""
+        uids, lengths = list(uids), list(lengths)
+        cfg = self._config.state_manager
+        cur_seqs = self._state_manager.n_tracked_sequences
+        free_blocks = int(self._state_manager.free_blocks[0])
+        batch_len = 0
+        if len(uids) > cfg.max_ragged_sequence_count:
+            return SchedulingResult.BatchSequenceLimitExceeded
+        for uid, length in zip(uids, lengths):
+            seq = self._state_manager.get_sequence(uid)
+            if seq is None:
+                cur_seqs += 1
+                seq = PlaceholderSequenceDescriptor()
+            if seq.seen_tokens + length > cfg.max_context:
+                return SchedulingResult.SequenceTokenLimitExceeded
+            sched_len, sched_blocks = self._model.get_kv_requirements(seq, length, free_blocks)
+            if sched_len != length:
+                return SchedulingResult.KVCacheLimitExceeded
+            batch_len += length
+            free_blocks -= sched_blocks
+        if cur_seqs > cfg.max_tracked_sequences:
+            return SchedulingResult.EngineSequenceLimitExceeded
+        if batch_len > cfg.max_ragged_batch_size:
+            return SchedulingResult.BatchTokenLimitExceeded
+        return SchedulingResult.Success
+
+    def get_remaining_block_capacity(self, uid: int) -> int:
+        seq = self._state_manager.get_sequence(uid)
+        if seq is None:
+            return 0
+        return self._model.get_remaining_block_capacity(seq)
+
+    def flush(self, uid: int) -> None:
+        """Remove all state of a sequence and release its KV blocks."""
+        self._state_manager.flush_sequence(uid)
+
+    # ------------------------------------------------------------------------------------------------
+    # serialisation (ref: engine_v2.py:284-301 + model_implementations/flat_model_helpers.py:59-282)
+    # ------------------------------------------------------------------------------------------------
+    def serialize(self, save_path: str) -> None:
+        from ...models.flat_model import flatten_model_weights, make_metadata_filename, make_param_filename
+        os.makedirs(save_path, exist_ok=True)
+        rank, size = self._model.tp_rank, self._model.tp_size
+        flat, meta = flatten_model_weights(self._model.w)
+        torch.save(flat.cpu(), make_param_filename(save_path, rank, size))
+        with open(make_metadata_filename(save_path, rank, size), "w") as f:
+            json.dump(meta, f)
+        if rank == 0:
+            with open(os.path.join(save_path, "ds_model_config.pkl"), "wb") as f:
+                pickle.dump({"arch": self._model.spec, "dtype": str(self._model.dtype).replace("torch.", "")}, f)

@@ -1,0 +1,408 @@
+"""The single model executor: runs any :class:`ArchSpec` over a ragged batch.
+
+Plays the role of the reference's ``DSTransformerModelBase`` + per-family ``model.py``
+(``deepspeed/inference/v2/model_implementations/inference_transformer_base.py:48-623``,
+``llama_v2/model.py:118-252``, ``opt/model.py:101-197`` ...). Design points:
+
+* All activations live in buffers sized once for ``max_ragged_batch_size`` tokens.
+* Kernel count per layer (dense, no TP): norm -> QKV(+RoPE+KV append) -> attention -> O-proj ->
+  norm -> up(+act/gate) -> down. Residual adds never run as kernels of their own: a row-parallel
+  GEMM leaves its result as a *pending delta* (16-bit, or fp32 partial sums when split-K /
+  tensor-parallel) and the next norm kernel folds it into the residual stream while normalising.
+* HCache capture is free: with capture on, the attention-norm kernel of layer ``l`` writes its output
+  straight into ``latent_buf[l]`` — the QKV GEMM reads it from there — so "saving the hidden states"
+  is one async D2H of that buffer (the reference allocates a fresh ``[L, T, H]`` tensor per forward,
+  copies every layer into it and then blocks on ``.cpu()``: ``llama_v2/model.py:203-220``).
+* HCache restore projects ONLY K and V (a row-slice view of ``w_qkv``; the reference runs the full QKV
+  GEMM and discards Q, ``llama_v2/model.py:239``), fused with RoPE and the paged write, and is
+  layer-pipelined against the H2D stream with a ring of staging slots and reused events.
+"""
+from __future__ import annotations
+
+from typing import List, Optional, Sequence, Tuple
+
+import torch
+
+from ..inference.v2.ragged import DSStateManager, KVCacheConfig, RaggedBatchWrapper
+from ..inference.v2.ragged.manager_configs import DSStateManagerConfig
+from ..ops import reference as ref
+from ..ops.backend import MAX_DECODE_SPLITS, get_ops, pick_decode_splits
+from ..ops.kernels import ACT_CODES
+from .arch import ArchSpec
+from .weights import ModelWeights, shard_info
+
+#: row-parallel GEMMs switch from fp32 partial-sum accumulation (split-K) to plain 16-bit stores above this
+ACCUM_MAX_TOKENS = 256
+#: staging slots of the restore pipeline (H2D of layer l+1.. overlaps the projection of layer l)
+RESTORE_SLOTS = 3
+
+
+def ceil_div(a: int, b: int) -> int:
+    return -(-a // b)
+
+
+class TPComm:
+    """How row-parallel partial sums meet across tensor-parallel ranks (see parallel/tp_comm.py)."""
+    fused = False
+
+    def __init__(self, group=None, size: int = 1, rank: int = 0):
+        self.group, self.size, self.rank = group, size, rank
+
+    def all_reduce_delta(self, delta32: torch.Tensor) -> None:
+        if self.size > 1:
+            import torch.distributed as dist
+            dist.all_reduce(delta32, group=self.group)
+
+    def all_gather_logits(self, local: torch.Tensor, out_full: torch.Tensor, vocab_ranges) -> torch.Tensor:
+        import torch.distributed as dist
+        if all((b - a) == (vocab_ranges[0][1] - vocab_ranges[0][0]) for a, b in vocab_ranges):
+            parts = torch.empty((self.size, ) + tuple(local.shape), dtype=local.dtype, device=local.device)
+            dist.all_gather_into_tensor(parts, local.contiguous(), group=self.group)
+            out_full.copy_(parts.permute(1, 0, 2).reshape(local.shape[0], -1))
+        else:
+            parts = [torch.empty((local.shape[0], b - a), dtype=local.dtype, device=local.device) for a, b in vocab_ranges]
+            dist.all_gather(parts, local.contiguous(), group=self.group)
+            out_full.copy_(torch.cat(parts, dim=1))
+        return out_full
+
+
+class RaggedTransformer:
+
+    def __init__(self, spec: ArchSpec, weights: ModelWeights, state_config: DSStateManagerConfig,
+                 dtype: torch.dtype = torch.bfloat16, device: Optional[torch.device] = None, tp_rank: int = 0,
+                 tp_size: int = 1, comm: Optional[TPComm] = None, capture_latents: bool = True) -> None:
+        self.spec, self.w, self.dtype = spec, weights, dtype
+        self.device = device if device is not None else weights.embed.device
+        self.tp_rank, self.tp_size = tp_rank, tp_size
+        self.comm = comm if comm is not None else TPComm(size=tp_size, rank=tp_rank)
+        self.info = shard_info(spec, tp_rank, tp_size)
+        self.ops = get_ops(self.device)
+        self._state_config = state_config
+        self._state_manager: Optional[DSStateManager] = None
+        self.capture_enabled = capture_latents
+        self.n_q, self.n_kv, self.d = self.info.n_q, self.info.n_kv, spec.head_dim
+        self.scale = spec.attn_scale if spec.attn_scale is not None else ref.attention_scale(spec.head_dim)
+        self.act = ACT_CODES.get(spec.act, None)
+        if self.act is None:
+            raise ValueError(f"unsupported activation {spec.act}")
+        self.inv_freq = None
+        if spec.pos_emb == "rope":
+            self.inv_freq = self._make_inv_freq().to(self.device)
+        self._alloc_buffers()
+
+    # ------------------------------------------------------------------------------------------------
+    # construction helpers
+    # ------------------------------------------------------------------------------------------------
+    def _make_inv_freq(self) -> torch.Tensor:
+        s = self.spec
+        inv = ref.default_inv_freq(s.rot_dim, s.rope_theta)
+        rs = s.rope_scaling or {}
+        kind = rs.get("rope_type", rs.get("type"))
+        if kind == "linear":
+            inv = inv / float(rs.get("factor", 1.0))
+        elif kind == "llama3":
+            import math
+            factor, lo, hi = rs.get("factor", 8.0), rs.get("low_freq_factor", 1.0), rs.get("high_freq_factor", 4.0)
+            old = rs.get("original_max_position_embeddings", 8192)
+            wavelen = 2 * math.pi / inv
+            smooth = ((old / wavelen) - lo) / (hi - lo)
+            scaled = torch.where(wavelen > old / lo, inv / factor, inv)
+            mid = (wavelen <= old / lo) & (wavelen >= old / hi)
+            inv = torch.where(mid, (1 - smooth) * inv / factor + smooth * inv, scaled)
+        return inv.float()
+
+    @property
+    def kv_block_size(self) -> int:
+        return 128 if self.d <= 64 else 64
+
+    def _alloc_buffers(self) -> None:
+        s, c = self.spec, self._state_config
+        T, S, H = c.max_ragged_batch_size, c.max_ragged_sequence_count, s.hidden
+        dev, dt = self.device, self.dtype
+
+        def buf(*shape, dtype=dt):
+            return torch.zeros(shape, dtype=dtype, device=dev)
+
+        inter = max(self.info.inter, self.info.moe_inter_range[1] - self.info.moe_inter_range[0],
+                    self.info.shared_inter_range[1] - self.info.shared_inter_range[0])
+        qkv_cols = (self.n_q + 2 * self.n_kv) * self.d
+        self.residual = buf(T, H)
+        self.xn = buf(T, H)
+        self.xn2 = buf(T, H)
+        self.latent_buf = buf(s.n_layers, T, H) if self.capture_enabled else None
+        self.qkv_buf = buf(T, qkv_cols)
+        self.q_buf = buf(T, self.n_q * self.d)
+        self.attn_buf = buf(T, self.n_q * self.d)
+        self.act_buf = buf(T, inter)
+        self.delta32 = buf(T, H, dtype=torch.float32)
+        self.delta16 = buf(T, H)
+        self.hidden_last = buf(S, H)
+        self.logits_local = buf(S, self.info.vocab)
+        self.logits_full = buf(S, s.vocab) if self.tp_size > 1 else None
+        self.kv_scratch = None
+        self.ws_gemm = self.ws_small = self.ws_large = None
+        self.io_stream = None
+        if dev.type == "cuda":
+            k = self.ops.k
+            n_max = max(qkv_cols, (2 if s.gated_mlp else 1) * inter, self.info.vocab, H)
+            self.ws_gemm = torch.zeros(k.gemm_splitk_workspace_bytes(128, n_max), dtype=torch.uint8, device=dev)
+            G = max(1, self.n_q // max(1, self.n_kv))
+            rows = min(8, max(1, (8 // G) * G))
+            worst = 16
+            for n in sorted({1, 2, 4, 8, 16, 32, 64, 128, 256, S}):
+                if n <= S:
+                    worst = max(worst, k.splitkv_workspace_bytes(n, self.n_q, self.n_kv, self.d,
+                                                                 pick_decode_splits(n, self.n_kv, 1 << 30), rows))
+            worst = max(worst, k.splitkv_workspace_bytes(S, self.n_q, self.n_kv, self.d, 1, rows))
+            self.ws_small = torch.zeros(worst, dtype=torch.uint8, device=dev)
+            worst_l = 16
+            for n in range(1, 149):
+                units = n * self.n_q
+                if units >= 148:
+                    break
+                sp = min(16, -(-148 // units))
+                worst_l = max(worst_l, k.prefill_workspace_bytes(n, self.n_q, self.d, sp))
+            self.ws_large = torch.zeros(worst_l, dtype=torch.uint8, device=dev)
+            self.io_stream = torch.cuda.Stream(device=dev)
+            self.restore_stage = buf(RESTORE_SLOTS, T, H)
+            self.ev_loaded = [torch.cuda.Event() for _ in range(RESTORE_SLOTS)]
+            self.ev_consumed = [torch.cuda.Event() for _ in range(RESTORE_SLOTS)]
+            if not (self.d in (64, 128) and (self.inv_freq is None or s.rot_dim == self.d)):
+                self.kv_scratch = buf(T, 2 * self.n_kv * self.d)
+
+    # ------------------------------------------------------------------------------------------------
+    # DSInferenceModelBase-style KV accounting (ref: inference_transformer_base.py:336-387)
+    # ------------------------------------------------------------------------------------------------
+    def kv_cache_config(self) -> Tuple[KVCacheConfig, ...]:
+        bs = self.kv_block_size
+        max_blocks = ceil_div(self._state_config.max_context, bs)
+        return (KVCacheConfig(block_size=bs, cache_shape=(self.spec.n_layers, self.n_kv, self.d),
+                              cache_dtype=self.dtype, max_blocks_per_allocation_group=max_blocks), )
+
+    def set_state_manager(self, state_manager: DSStateManager) -> None:
+        self._state_manager = state_manager
+
+    @property
+    def state_manager(self) -> DSStateManager:
+        return self._state_manager
+
+    def get_kv_requirements(self, sequence, max_new_tokens: int, max_new_blocks) -> Tuple[int, int]:
+        max_new_blocks = int(max_new_blocks.reshape(-1)[0]) if isinstance(max_new_blocks, torch.Tensor) else int(max_new_blocks)
+        bs = self.kv_block_size
+        total = sequence.seen_tokens + max_new_tokens
+        need = ceil_div(total, bs) - sequence.cur_allocated_blocks
+        if need <= max_new_blocks:
+            return max_new_tokens, max(need, 0)
+        capacity = (max_new_blocks + sequence.cur_allocated_blocks) * bs - sequence.seen_tokens
+        return max(capacity, 0), max_new_blocks
+
+    def get_remaining_block_capacity(self, sequence) -> int:
+        return (-sequence.seen_tokens) % self.kv_block_size
+
+    def maybe_allocate_kv(self, sequence, n_new_tokens: int) -> None:
+        free = self._state_manager.free_blocks
+        _, n_blocks = self.get_kv_requirements(sequence, n_new_tokens, free)
+        if n_blocks > 0:
+            sequence.extend_kv_cache(self._state_manager.allocate_blocks(n_blocks))
+
+    def maybe_free_kv(self, sequence) -> None:
+        """Dense attention keeps every block until the sequence is flushed."""
+        return
+
+    def prepare_batch(self, batch: RaggedBatchWrapper) -> None:
+        """Attention work items are produced by ``batch.finalize`` (native); nothing left to do here."""
+        return
+
+    # ------------------------------------------------------------------------------------------------
+    # forward
+    # ------------------------------------------------------------------------------------------------
+    def _row_parallel(self, x: torch.Tensor, w: torch.Tensor, b: Optional[torch.Tensor], T: int, force_accum: bool,
+                      last_into_delta: bool = True) -> torch.Tensor:
+        """y = x @ w.T (+b), left as the pending delta. fp32 partial sums when the GEMM is split over K or ranks."""
+        if force_accum or T <= ACCUM_MAX_TOKENS or self.tp_size > 1:
+            d32 = self.delta32[:T]
+            self.ops.gemm_accum(x, w, d32, bias=b, comm=self.comm)
+            if self.tp_size > 1 and last_into_delta:
+                self.comm.all_reduce_delta(d32)
+            return d32
+        return self.ops.gemm(x, w, self.delta16[:T], bias=b)
+
+    def _mlp(self, x: torch.Tensor, lw, T: int, force_accum: bool) -> torch.Tensor:
+        s = self.spec
+        if s.is_moe:
+            return self._moe(x, lw, T)
+        n_act = lw.w_up.shape[0] // (2 if s.gated_mlp else 1)
+        act = self.act_buf[:T, :n_act]
+        self.ops.gemm(x, lw.w_up, act, bias=lw.b_up, act=self.act, gated=s.gated_mlp, workspace=self.ws_gemm)
+        return self._row_parallel(act, lw.w_down, lw.b_down, T, force_accum)
+
+    def _moe(self, x: torch.Tensor, lw, T: int) -> torch.Tensor:
+        """Top-k mixture of experts (tensor-parallel experts, no expert parallelism — as the reference's v2:
+        ``inference_transformer_base.py:588``). Routing runs on the small [T, E] score matrix; expert GEMMs
+        accumulate straight into the fp32 pending delta scaled by their gate weight.
+        Ref: modules/implementations/moe/cutlass_multi_gemm.py:28-249, ragged_ops/top_k_gating."""
+        s = self.spec
+        d32 = self.delta32[:T]
+        scores = ref.gemm(x, lw.w_router, out_dtype=torch.float32) if self.device.type == "cpu" else \
+            self.ops.k.gemm(x, lw.w_router).float()
+        probs = torch.softmax(scores, dim=-1)
+        topv, topi = torch.topk(probs, s.top_k, dim=-1)
+        if s.norm_topk_prob:
+            topv = topv / topv.sum(-1, keepdim=True)
+        mult = 2 if s.gated_mlp else 1
+        for e, ew in enumerate(lw.experts):
+            sel = (topi == e)
+            rows = sel.any(-1).nonzero(as_tuple=False).flatten()
+            if rows.numel() == 0:
+                continue
+            gate_w = (topv * sel).sum(-1)[rows]
+            xe = x.index_select(0, rows)
+            he = torch.empty((rows.numel(), ew.w_up.shape[0] // mult), dtype=x.dtype, device=x.device)
+            self.ops.gemm(xe, ew.w_up, he, act=self.act, gated=s.gated_mlp)
+            ye = torch.empty((rows.numel(), s.hidden), dtype=x.dtype, device=x.device)
+            self.ops.gemm(he, ew.w_down, ye)
+            d32.index_add_(0, rows, ye.float() * gate_w[:, None])
+        if lw.shared_expert is not None:
+            se = lw.shared_expert
+            hs = torch.empty((T, se.w_up.shape[0] // mult), dtype=x.dtype, device=x.device)
+            self.ops.gemm(x, se.w_up, hs, act=self.act, gated=s.gated_mlp)
+            ys = torch.empty((T, s.hidden), dtype=x.dtype, device=x.device)
+            self.ops.gemm(hs, se.w_down, ys)
+            g = torch.sigmoid(ref.gemm(x, lw.w_shared_gate, out_dtype=torch.float32))
+            d32 += ys.float() * g
+        if self.tp_size > 1:
+            self.comm.all_reduce_delta(d32)
+        return d32
+
+    def forward(self, batch: RaggedBatchWrapper, capture: bool = False) -> Tuple[torch.Tensor, Optional[torch.Tensor]]:
+        """One ragged forward. Returns ``(logits [n_seqs, vocab], latents)`` where latents is the device view
+        ``[n_layers, n_tokens, hidden]`` of the captured QKV inputs (None when capture is off)."""
+        s, w, ops = self.spec, self.w, self.ops
+        T, S = batch.current_tokens, batch.current_sequences
+        if capture and self.latent_buf is None:
+            raise RuntimeError("hidden-state capture was disabled when the model was built")
+        pos, slot = batch.tok_pos(), batch.tok_slot()
+        resid = self.residual[:T]
+        ops.embed(batch.input_ids(), w.embed, resid, pos_weight=w.pos_embed, tok_pos=pos, pos_offset=s.learned_pos_offset)
+        ln = s.norm == "layer"
+        pending = None
+        kv = self._state_manager
+        bs = kv.kv_block_size
+        two_norms = (not s.parallel_residual) or s.parallel_two_norms
+        for li in range(s.n_layers):
+            lw = w.layers[li]
+            xn = (self.latent_buf[li] if capture else self.xn)[:T]
+            ops.norm(resid, lw.norm1_g, xn, beta=lw.norm1_b, delta=pending, zero_delta=True,
+                     res_out=resid if pending is not None else None, eps=s.norm_eps, layer_norm=ln)
+            kv_layer = kv.get_cache(li)
+            ops.qkv_rope_kv_append(xn, lw.w_qkv, lw.b_qkv, self.qkv_buf[:T], self.q_buf[:T], kv_layer, pos, slot,
+                                   self.inv_freq, self.n_q, self.n_kv, self.d, s.rot_dim, bs, workspace=self.ws_gemm)
+            attn = self.attn_buf[:T]
+            ops.attention(self.q_buf[:T], attn, kv_layer, batch, self.n_q, self.n_kv, self.d, self.scale,
+                          ws_small=self.ws_small, ws_large=self.ws_large)
+            if s.parallel_residual:
+                xm = xn
+                if two_norms:
+                    xm = ops.norm(resid, lw.norm2_g, self.xn2[:T], beta=lw.norm2_b, eps=s.norm_eps, layer_norm=ln)
+                self._row_parallel(attn, lw.w_o, lw.b_o, T, force_accum=True, last_into_delta=False)
+                pending = self._mlp(xm, lw, T, force_accum=True)
+            else:
+                d1 = self._row_parallel(attn, lw.w_o, lw.b_o, T, force_accum=False)
+                x2 = ops.norm(resid, lw.norm2_g, self.xn2[:T], beta=lw.norm2_b, delta=d1, zero_delta=True, res_out=resid,
+                              eps=s.norm_eps, layer_norm=ln)
+                pending = self._mlp(x2, lw, T, force_accum=False)
+        # ---- last-token logits ----
+        fin = self.xn2[:T]
+        if s.final_norm:
+            ops.norm(resid, w.final_norm_g, fin, beta=w.final_norm_b, delta=pending, zero_delta=True, eps=s.norm_eps,
+                     layer_norm=ln)
+        else:
+            ones = torch.ones(s.hidden, dtype=self.dtype, device=self.device)
+            ops.norm(resid, ones, self.xn[:T], delta=pending, zero_delta=True, res_out=fin, eps=s.norm_eps)
+        hidden = ops.gather_rows(fin, batch.last_rows(), self.hidden_last[:S])
+        logits = ops.gemm(hidden, w.lm_head, self.logits_local[:S], bias=w.lm_head_b, workspace=self.ws_gemm)
+        if self.tp_size > 1:
+            ranges = [shard_info(s, r, self.tp_size).vocab_range for r in range(self.tp_size)]
+            logits = self.comm.all_gather_logits(logits, self.logits_full[:S], ranges)
+        return logits, (self.latent_buf[:, :T] if capture else None)
+
+    # ------------------------------------------------------------------------------------------------
+    # HCache restore
+    # ------------------------------------------------------------------------------------------------
+    def kv_weight(self, li: int) -> Tuple[torch.Tensor, Optional[torch.Tensor]]:
+        """[W_k; W_v] (and bias) of a layer: row-slice views of the fused QKV parameters (no copy)."""
+        lw = self.w.layers[li]
+        r0 = self.n_q * self.d
+        return lw.w_qkv[r0:], (lw.b_qkv[r0:] if lw.b_qkv is not None else None)
+
+    def restore_kv(self, batch: RaggedBatchWrapper, latents: Sequence[torch.Tensor],
+                   layers: Optional[Sequence[int]] = None) -> None:
+        """Rebuild the paged K/V of the batch's tokens from saved hidden states.
+
+        ``latents``: one host tensor per sequence of the batch, ``[n_saved_layers, n_tokens_i, hidden]``, whose
+        leading axis follows ``layers`` (default: every layer). Pinned tensors stream asynchronously; pageable
+        ones go through the driver's staging path. Returns without waiting for the projections; kernels of the
+        next ``put`` queue behind them on the same stream.
+        """
+        s, ops = self.spec, self.ops
+        layers = list(range(s.n_layers)) if layers is None else list(layers)
+        T = batch.current_tokens
+        if sum(int(l.shape[1]) for l in latents) != T:
+            raise ValueError("latents do not cover the tokens of the restore batch")
+        pos, slot = batch.tok_pos(), batch.tok_slot()
+        kv = self._state_manager
+        bs = kv.kv_block_size
+        if self.device.type != "cuda":
+            for i, li in enumerate(layers):
+                lat = torch.cat([l[i] for l in latents], dim=0).to(self.dtype)
+                wk, bk = self.kv_weight(li)
+                ops.restore_kv_proj(lat, wk, bk, kv.get_cache(li), pos, slot, self.inv_freq, self.n_kv, self.d, s.rot_dim, bs)
+            return
+        comp = torch.cuda.current_stream()
+        io = self.io_stream
+        io.wait_stream(comp)  # staging slots may still feed kernels of an earlier restore
+        for i, li in enumerate(layers):
+            k = i % RESTORE_SLOTS
+            stage = self.restore_stage[k]
+            with torch.cuda.stream(io):
+                if i >= RESTORE_SLOTS:
+                    io.wait_event(self.ev_consumed[k])
+                off = 0
+                for lat in latents:
+                    n = int(lat.shape[1])
+                    stage[off:off + n].copy_(lat[i], non_blocking=True)
+                    off += n
+                self.ev_loaded[k].record(io)
+            comp.wait_event(self.ev_loaded[k])
+            wk, bk = self.kv_weight(li)
+            ops.restore_kv_proj(stage[:T], wk, bk, kv.get_cache(li), pos, slot, self.inv_freq, self.n_kv, self.d,
+                                s.rot_dim, bs, scratch=self.kv_scratch[:T] if self.kv_scratch is not None else None)
+            self.ev_consumed[k].record(comp)
+
+    def restore_kv_pages(self, block_ids: torch.Tensor, kv_host: torch.Tensor, layers: Sequence[int]) -> None:
+        """Plain KV reload for the layers the planner assigned to KV offload: ``kv_host`` is
+        ``[n_blocks, len(layers), 2, kvh, bs, d]`` (host), written into ``block_ids`` of each listed layer."""
+        kv = self._state_manager.kv_cache
+        cache = kv.full_cache
+        ids = block_ids.to(torch.int32)
+        if self.device.type != "cuda":
+            for j, li in enumerate(layers):
+                cache[li, ids.long()] = kv_host[:, j].to(cache.dtype)
+            return
+        ids_dev = ids.to(self.device, non_blocking=True)
+        comp = torch.cuda.current_stream()
+        io = self.io_stream
+        io.wait_stream(comp)
+        with torch.cuda.stream(io):
+            staged = kv_host.to(self.device, non_blocking=True)
+            done = torch.cuda.Event()
+            done.record(io)
+        comp.wait_event(done)
+        staged.record_stream(comp)
+        for j, li in enumerate(layers):
+            self.ops.k.kv_blocks_copy(cache[li:li + 1], staged[:, j:j + 1].contiguous() if len(layers) > 1 else staged,
+                                      ids_dev, to_staging=False)
+
+    # ------------------------------------------------------------------------------------------------
+    def n_params_local(self) -> int:
+        return sum(t.numel() for t in self.w.named_tensors().values())
