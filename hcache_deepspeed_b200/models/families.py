@@ -94,6 +94,16 @@ def map_llama_like(name: str, t: torch.Tensor, spec: ArchSpec) -> List[Piece]:
             return [(layer, "mlp.gate", g), (layer, "mlp.up", u)]
         if sub == "gate" and kind == "weight":  # MoE router
             return [(layer, "moe.router", t)]
+        if sub == "experts" and len(parts) == 3 and t.dim() == 3:
+            # transformers >= 5 keeps experts fused: gate_up_proj [E, 2I, H] (rows [gate; up]), down_proj [E, H, I]
+            out: List[Piece] = []
+            for e in range(t.shape[0]):
+                if parts[2] == "gate_up_proj":
+                    g, u = t[e].chunk(2, dim=0)
+                    out += [(layer, f"moe.experts.{e}.gate", g), (layer, f"moe.experts.{e}.up", u)]
+                elif parts[2] == "down_proj":
+                    out.append((layer, f"moe.experts.{e}.down", t[e]))
+            return out
         if sub == "experts" and len(parts) >= 5:
             e, proj = int(parts[2]), parts[3]
             table = {"w1": "gate", "w3": "up", "w2": "down", "gate_proj": "gate", "up_proj": "up", "down_proj": "down"}

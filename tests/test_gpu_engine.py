@@ -45,7 +45,7 @@ def test_restore_equals_live_kv_llama7b_shapes():
     _, l1 = eng.put([1], [p1])
     _, l2 = eng.put([1], [p2])  # second chunk of the same sequence
     saved = torch.cat([l1[0], l2[0]], dim=1)
-    assert saved.shape == (2, 745, spec.hidden) and saved.is_pinned()
+    assert saved.shape == (2, 745, spec.hidden) and l1[0].is_pinned()
     eng.restore_kv([9], [torch.cat([p1, p2])], [saved])
     kv = eng.state_manager.kv_cache.full_cache
     s1, s9 = eng.state_manager.get_sequence(1), eng.state_manager.get_sequence(9)
