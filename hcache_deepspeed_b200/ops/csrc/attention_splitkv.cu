@@ -390,3 +390,115 @@ extern "C" int hds_paged_attention_splitkv(const void* q, void* out, const void*
         return dtype == 0 ? dispatch_rows<128, true>(R, tm, a, n_items, s) : dispatch_rows<128, false>(R, tm, a, n_items, s);
     return dtype == 0 ? dispatch_rows<64, true>(R, tm, a, n_items, s) : dispatch_rows<64, false>(R, tm, a, n_items, s);
 }
+
+// =================================================================================================
+// hds_paged_attention_splitkv_static — the same split-KV attention, for callers that must not allocate
+// =================================================================================================
+// Some users of this library cannot hand it a scratch buffer because they have no way to obtain one:
+// a serving process that gave every free byte of HBM to the KV cache at start-up (RESERVE mode does
+// exactly that) has nothing left to cudaMalloc from; a C or C++ host that embeds the library without
+// PyTorch has no caching allocator to borrow from; and latency-critical loops cannot afford cudaMalloc
+// at all, because it synchronises the whole device. For them the partial (O, m, l) results and the
+// per-(item, kv head) arrival counters live in the fixed array below instead of caller memory.
+//
+// Cost and limits, so nobody is surprised:
+//   * the array is part of the library image: every GPU that loads libhds_b200.so holds
+//     HDS_STATIC_SCRATCH_BYTES (8 MiB) of device memory until the process exits, used or not;
+//   * a problem whose scratch need (hds_paged_attention_splitkv_workspace_bytes) exceeds that size is
+//     refused with HDS_ERR_TOO_LARGE (-4) and a message saying how much was needed — lower n_splits or
+//     n_items, or use the caller-scratch entry point;
+//   * every call on a device shares the one array and finds whatever the previous call left in it. The
+//     arrival counters are therefore cleared on the caller's stream at the start of each call (the layout
+//     depends on n_items, so an earlier call's partial sums may sit where this call's counters go);
+//     nothing else needs a defined starting value;
+//   * because the array is shared, two calls that overlap in time on the same GPU (different streams, or
+//     different host threads) race on it and produce garbage. Serialise them on one stream;
+//   * the first call on each device looks up the array's device address (see below). Make that first
+//     call during start-up, before any stream capture is begun on that device.
+//
+// In host code the identifier g_splitkv_static_scratch is only a stand-in for the symbol: taking its
+// address there yields a host pointer that kernels must never see. The device address is fetched once
+// per device, with that device current, through cudaGetSymbolAddress and passed to the kernel.
+#define HDS_STATIC_SCRATCH_BYTES (8 * 1024 * 1024)
+static __device__ __align__(256) unsigned char g_splitkv_static_scratch[HDS_STATIC_SCRATCH_BYTES];
+
+namespace hds {
+static int static_scratch_address(char** out) {
+    static void* addr[64] = {nullptr};
+    static std::mutex mu;
+    int dev = 0;
+    HDS_CHECK_CUDA(cudaGetDevice(&dev));
+    if (dev < 0 || dev >= 64) {
+        set_error("hds_paged_attention_splitkv_static: device ordinal out of range");
+        return HDS_ERR_BAD_ARG;
+    }
+    std::lock_guard<std::mutex> lock(mu);
+    if (addr[dev] == nullptr) {
+        void* p = nullptr;
+        HDS_CHECK_CUDA(cudaGetSymbolAddress(&p, g_splitkv_static_scratch));  // device `dev` is current
+        addr[dev] = p;
+    }
+    *out = static_cast<char*>(addr[dev]);
+    return HDS_OK;
+}
+}  // namespace hds
+
+extern "C" int64_t hds_paged_attention_splitkv_static_capacity(void) { return HDS_STATIC_SCRATCH_BYTES; }
+
+extern "C" int hds_paged_attention_splitkv_static(const void* q, void* out, const void* kv_cache_layer,
+                                                  int64_t num_blocks, const int32_t* block_tables,
+                                                  int max_blocks_per_seq, const hds_attn_item* items, int n_items,
+                                                  int rows_per_item, int n_q_heads, int n_kv_heads, int head_dim,
+                                                  int block_size, int n_splits, float scale, int dtype, void* stream) {
+    HDS_REQUIRE(head_dim == 64 || head_dim == 128, "paged_attention_splitkv_static: head_dim must be 64 or 128");
+    HDS_REQUIRE(block_size == 16 || block_size == 32 || block_size == 64 || block_size == 128,
+                "paged_attention_splitkv_static: block_size must be 16/32/64/128");
+    HDS_REQUIRE(n_kv_heads > 0 && n_q_heads % n_kv_heads == 0,
+                "paged_attention_splitkv_static: n_q_heads % n_kv_heads != 0");
+    HDS_REQUIRE(rows_per_item >= 1 && rows_per_item <= 8, "paged_attention_splitkv_static: at most 8 query rows per item");
+    HDS_REQUIRE(n_splits >= 1 && n_splits <= 64, "paged_attention_splitkv_static: n_splits in [1,64]");
+    HDS_REQUIRE(dtype == 0 || dtype == 1, "paged_attention_splitkv_static: dtype must be 0 (bf16) or 1 (fp16)");
+    if (n_items == 0) return HDS_OK;
+    const int64_t need =
+        hds_paged_attention_splitkv_workspace_bytes(n_items, n_q_heads, n_kv_heads, head_dim, n_splits, rows_per_item);
+    if (need > HDS_STATIC_SCRATCH_BYTES) {
+        char b[256];
+        snprintf(b, sizeof(b),
+                 "paged_attention_splitkv_static: this problem needs %lld bytes of scratch but the built-in array holds "
+                 "%d; reduce n_splits / n_items or call hds_paged_attention_splitkv with your own scratch",
+                 static_cast<long long>(need), HDS_STATIC_SCRATCH_BYTES);
+        set_error(b);
+        return HDS_ERR_TOO_LARGE;
+    }
+    char* ws = nullptr;
+    int rc = static_scratch_address(&ws);
+    if (rc) return rc;
+    cudaStream_t s = static_cast<cudaStream_t>(stream);
+    const int R = rows_bucket(rows_per_item);
+    const int64_t units = static_cast<int64_t>(n_items) * n_kv_heads;
+    // the counters must read zero when the kernel starts; the previous call may have left partial sums here
+    HDS_CHECK_CUDA(cudaMemsetAsync(ws, 0, static_cast<size_t>(align256(units * 4)), s));
+    AttnArgs a;
+    memset(&a, 0, sizeof(a));
+    a.q = q;
+    a.out = out;
+    a.block_tables = block_tables;
+    a.items = items;
+    a.max_blocks_per_seq = max_blocks_per_seq;
+    a.n_q_heads = n_q_heads;
+    a.n_kv_heads = n_kv_heads;
+    a.block_size = block_size;
+    a.n_splits = n_splits;
+    a.scale_log2 = scale * 1.4426950408889634f;
+    a.counters = reinterpret_cast<int32_t*>(ws);
+    a.ws_ml = reinterpret_cast<float*>(ws + align256(units * 4));
+    a.ws_o = reinterpret_cast<float*>(ws + align256(units * 4) + align256(units * n_splits * R * 2 * 4));
+    CUtensorMap tm;
+    const uint64_t rows = static_cast<uint64_t>(num_blocks) * 2 * n_kv_heads * block_size;
+    rc = make_tmap_2d_16b(&tm, kv_cache_layer, head_dim, rows, static_cast<uint64_t>(head_dim) * 2, 64, block_size,
+                          dtype == 0);
+    if (rc) return rc;
+    if (head_dim == 128)
+        return dtype == 0 ? dispatch_rows<128, true>(R, tm, a, n_items, s) : dispatch_rows<128, false>(R, tm, a, n_items, s);
+    return dtype == 0 ? dispatch_rows<64, true>(R, tm, a, n_items, s) : dispatch_rows<64, false>(R, tm, a, n_items, s);
+}

@@ -133,6 +133,24 @@ int hds_paged_attention_splitkv(const void* q, void* out, const void* kv_cache_l
                                 int block_size, int n_splits, float scale, void* workspace, int64_t workspace_bytes,
                                 int dtype, void* stream);
 
+/* Split-KV paged attention that allocates nothing and takes no scratch pointer: the partial results and the
+ * arrival counters live in a fixed 8 MiB device array that is part of the library image
+ * (hds_paged_attention_splitkv_static_capacity() bytes, held by every GPU that loads the library until exit).
+ * Meant for callers that cannot obtain scratch memory: processes that handed all free HBM to the KV cache,
+ * C/C++ hosts without an allocator to borrow from, loops that cannot tolerate cudaMalloc's device-wide sync.
+ * Same arguments and results as hds_paged_attention_splitkv minus workspace / workspace_bytes.
+ * Returns -4 (HDS_ERR_TOO_LARGE) with an explanatory hds_last_error() when the problem needs more scratch
+ * than the array holds. The array is shared by every call on the device: calls that overlap on the GPU race;
+ * issue them on one stream. The first call on a device resolves the array's device address — make it during
+ * start-up, before any stream capture begins on that device.
+ * This entry point has no counterpart in the reference. */
+int64_t hds_paged_attention_splitkv_static_capacity(void);
+int hds_paged_attention_splitkv_static(const void* q, void* out, const void* kv_cache_layer, int64_t num_blocks,
+                                       const int32_t* block_tables, int max_blocks_per_seq,
+                                       const hds_attn_item* items, int n_items, int rows_per_item, int n_q_heads,
+                                       int n_kv_heads, int head_dim, int block_size, int n_splits, float scale,
+                                       int dtype, void* stream);
+
 /* tcgen05 paged attention for items with up to 128 query tokens (prefill / chunked continuation): QK^T and
  * PV on the tensor cores with TMEM accumulators, TMA page gathers, online softmax in registers.
  * n_q_rows = total rows of q (bounds the Q tensor map). n_splits > 1 splits each item's KV range over several
