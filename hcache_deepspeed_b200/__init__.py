@@ -1,3 +1,75 @@
-"""hcache_deepspeed_b200 — a B200-native (sm_100a) LLM inference / serving framework with the
-capabilities of the HCache fork of DeepSpeed. See DESIGN.md for the architecture."""
+"""hcache_deepspeed_b200 — a B200-native (sm_100a) LLM inference / serving framework with the capabilities of
+the HCache fork of DeepSpeed. Top-level API mirrors ``deepspeed/__init__.py`` (``init_inference`` :291,
+``init_distributed`` :43, ``add_config_arguments`` :268, ``initialize`` :69). See DESIGN.md."""
+from __future__ import annotations
+
+import json
+from typing import Optional, Union
+
+from . import comm  # noqa: F401
+from .comm.comm import init_distributed  # noqa: F401
+from .utils.logging import log_dist, logger  # noqa: F401
 from .version import __version__  # noqa: F401
+
+__git_hash__ = None
+__git_branch__ = None
+
+
+def _parse_version(version_str: str):
+    import re
+    m = re.match(r"(\d+)\.(\d+)\.(\d+)", version_str)
+    return tuple(int(x) for x in m.groups()) if m else (0, 0, 0)
+
+
+__version_major__, __version_minor__, __version_patch__ = _parse_version(__version__)
+
+
+def init_inference(model, config=None, **kwargs):
+    """Initialize the inference engine (v1 API).
+
+    ``config`` may be a dict, a path to a JSON file, or None; keyword arguments are merged into it and a key given
+    both ways with different values is an error (same rule as ``deepspeed/__init__.py:341-362``).
+    Returns an :class:`hcache_deepspeed_b200.inference.engine.InferenceEngine`.
+    """
+    from .inference.config import DeepSpeedInferenceConfig
+    from .inference.engine import InferenceEngine
+    log_dist(f"hcache_deepspeed_b200 info: version={__version__}", ranks=[0])
+    if config is None:
+        config = {}
+    if isinstance(config, str):
+        with open(config, "r") as f:
+            config = json.load(f)
+    elif isinstance(config, DeepSpeedInferenceConfig):
+        config = config.model_dump(exclude_unset=True)
+    elif not isinstance(config, dict):
+        raise ValueError(f"'config' argument expected string or dictionary, got {type(config)}")
+    overlap = set(config.keys()).intersection(kwargs.keys())
+    for key in overlap:
+        if config[key] != kwargs[key]:
+            raise ValueError(f"Conflicting argument '{key}' in 'config':{config[key]} and kwargs:{kwargs[key]}")
+    config = dict(config)
+    config.update(kwargs)
+    return InferenceEngine(model, config=DeepSpeedInferenceConfig(**config))
+
+
+def add_config_arguments(parser):
+    """Add ``--deepspeed`` / ``--deepspeed_config`` (and the deprecated ``--deepscale*``) arguments."""
+    group = parser.add_argument_group("DeepSpeed", "DeepSpeed configurations")
+    group.add_argument("--deepspeed", default=False, action="store_true",
+                       help="Enable DeepSpeed (helper flag for user code, no impact on DeepSpeed backend)")
+    group.add_argument("--deepspeed_config", default=None, type=str, help="DeepSpeed json configuration file.")
+    group.add_argument("--deepscale", default=False, action="store_true",
+                       help="Deprecated enable DeepSpeed (helper flag for user code, no impact on DeepSpeed backend)")
+    group.add_argument("--deepscale_config", default=None, type=str, help="Deprecated DeepSpeed json configuration file.")
+    return parser
+
+
+def default_inference_config() -> dict:
+    from .inference.config import DeepSpeedInferenceConfig
+    return DeepSpeedInferenceConfig().model_dump()
+
+
+def initialize(*args, **kwargs):
+    """Training entry point (``deepspeed.initialize``): see :mod:`hcache_deepspeed_b200.runtime`."""
+    from .runtime.engine import initialize as _initialize
+    return _initialize(*args, **kwargs)

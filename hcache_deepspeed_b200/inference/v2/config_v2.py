@@ -39,6 +39,9 @@ class HCacheConfig(DeepSpeedConfigModel):
     'off': ``put`` returns ``None`` latents unless overridden per call."""
     capture_decode_steps: bool = True
     """Also capture single-token steps (needed if the generated tokens are to be restorable)."""
+    overlap_restore: bool = True
+    """``restore_kv`` defers its per-layer projections into the next ``put`` so the new turn's prefill overlaps the
+    host-to-device transfer of the saved hidden states."""
     host_ring_bytes: int = 2 << 30
     """Pinned host staging used for asynchronous capture."""
 

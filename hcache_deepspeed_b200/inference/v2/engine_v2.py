@@ -110,13 +110,17 @@ class InferenceEngineV2:
     # ------------------------------------------------------------------------------------------------
     def restore_kv(self, batch_uids: Iterable[int], batch_tokens: Iterable[torch.Tensor],
                    batch_latents: Iterable[Optional[Union[torch.Tensor, LatentHandle]]],
-                   layers: Optional[Sequence[int]] = None, do_checks: bool = True) -> None:
+                   layers: Optional[Sequence[int]] = None, do_checks: bool = True,
+                   defer: Optional[bool] = None) -> None:
         """Rebuild the KV cache of ``batch_uids`` from saved hidden states instead of recomputing the prompt.
 
         ``batch_tokens`` only supply the token counts (ref: engine_v2.py:108-128); ``batch_latents[i]`` is the host
         tensor ``[n_layers, n_tokens_i, hidden]`` returned by earlier ``put`` calls (concatenated along dim 1 by the
         caller if it spans several calls), or None to skip that uid. After the call the sequences have
         ``seen_tokens`` advanced; follow with a normal ``put`` of the new turn's tokens.
+
+        ``defer`` (default: ``hcache.overlap_restore``): only start the transfers now and let the next ``put``
+        interleave each layer's K/V projection with its own layers (hides the new turn's prefill under PCIe time).
         """
         uids, toks, lats = list(batch_uids), list(batch_tokens), list(batch_latents)
         todo = [(u, t, (l.wait() if isinstance(l, LatentHandle) else l)) for u, t, l in zip(uids, toks, lats)
@@ -137,7 +141,9 @@ class InferenceEngineV2:
             seq.pre_forward(tokens.numel())
             self._batch.insert_sequence(seq, tokens, do_checks=do_checks)
         self._batch.finalize()
-        self._model.restore_kv(self._batch, [l for _, _, l in todo], layers=layers)
+        if defer is None:
+            defer = self._config.hcache.overlap_restore
+        self._model.restore_kv(self._batch, [l for _, _, l in todo], layers=layers, defer=bool(defer))
         for uid, _, _ in todo:
             self._state_manager.get_sequence(uid).post_forward()
 
@@ -145,7 +151,7 @@ class InferenceEngineV2:
     # forward
     # ------------------------------------------------------------------------------------------------
     def put(self, batch_uids: Iterable[int], batch_tokens: Iterable[torch.Tensor], do_checks: bool = True,
-            capture_latents: Optional[bool] = None) -> Tuple[torch.Tensor, List]:
+            capture_latents: Optional[bool] = None, all_logits: bool = False) -> Tuple[torch.Tensor, List]:
         """One forward over a ragged batch. Returns ``(logits [len(batch_uids), vocab], latents)`` where
         ``latents[i]`` is sequence i's ``[n_layers, n_tokens_i, hidden]`` host tensor (pinned), a
         :class:`LatentHandle` in async mode, or None when capture is off."""
@@ -169,9 +175,9 @@ class InferenceEngineV2:
             capture = hc.enabled and hc.capture != "off"
             if capture and not hc.capture_decode_steps and self._batch.current_tokens == self._batch.current_sequences:
                 capture = False
-        logits, latent_dev = self._model.forward(self._batch, capture=bool(capture))
+        logits, latent_dev = self._model.forward(self._batch, capture=bool(capture), all_logits=all_logits)
         latents = self._export_latents(latent_dev) if capture else [None] * len(uids)
-        assert logits.shape[0] == self._batch.current_sequences
+        assert logits.shape[0] == (self._batch.current_tokens if all_logits else self._batch.current_sequences)
         for uid in uids:
             seq = self._state_manager.get_sequence(uid)
             seq.post_forward()
@@ -250,6 +256,7 @@ class InferenceEngineV2:
 
     def flush(self, uid: int) -> None:
         """Remove all state of a sequence and release its KV blocks."""
+        self._model.finish_pending_restore()  # a deferred restore may still target these blocks
         self._state_manager.flush_sequence(uid)
 
     # ------------------------------------------------------------------------------------------------

@@ -34,7 +34,7 @@ from .weights import ModelWeights, shard_info
 #: row-parallel GEMMs switch from fp32 partial-sum accumulation (split-K) to plain 16-bit stores above this
 ACCUM_MAX_TOKENS = 256
 #: staging slots of the restore pipeline (H2D of layer l+1.. overlaps the projection of layer l)
-RESTORE_SLOTS = 3
+RESTORE_SLOTS = 4
 
 
 def ceil_div(a: int, b: int) -> int:
@@ -79,6 +79,7 @@ class RaggedTransformer:
         self.ops = get_ops(self.device)
         self._state_config = state_config
         self._state_manager: Optional[DSStateManager] = None
+        self._pending_restore = None
         self.capture_enabled = capture_latents
         self.n_q, self.n_kv, self.d = self.info.n_q, self.info.n_kv, spec.head_dim
         self.scale = spec.attn_scale if spec.attn_scale is not None else ref.attention_scale(spec.head_dim)
@@ -165,6 +166,8 @@ class RaggedTransformer:
             self.ws_large = torch.zeros(worst_l, dtype=torch.uint8, device=dev)
             self.io_stream = torch.cuda.Stream(device=dev)
             self.restore_stage = buf(RESTORE_SLOTS, T, H)
+            self.restore_pos = torch.zeros(T, dtype=torch.int32, device=dev)
+            self.restore_slot = torch.zeros(T, dtype=torch.int32, device=dev)
             self.ev_loaded = [torch.cuda.Event() for _ in range(RESTORE_SLOTS)]
             self.ev_consumed = [torch.cuda.Event() for _ in range(RESTORE_SLOTS)]
             if not (self.d in (64, 128) and (self.inv_freq is None or s.rot_dim == self.d)):
@@ -274,9 +277,11 @@ class RaggedTransformer:
             self.comm.all_reduce_delta(d32)
         return d32
 
-    def forward(self, batch: RaggedBatchWrapper, capture: bool = False) -> Tuple[torch.Tensor, Optional[torch.Tensor]]:
+    def forward(self, batch: RaggedBatchWrapper, capture: bool = False,
+                all_logits: bool = False) -> Tuple[torch.Tensor, Optional[torch.Tensor]]:
         """One ragged forward. Returns ``(logits [n_seqs, vocab], latents)`` where latents is the device view
-        ``[n_layers, n_tokens, hidden]`` of the captured QKV inputs (None when capture is off)."""
+        ``[n_layers, n_tokens, hidden]`` of the captured QKV inputs (None when capture is off).
+        ``all_logits``: unembed every token instead of each sequence's last one (``[n_tokens, vocab]``; v1 API)."""
         s, w, ops = self.spec, self.w, self.ops
         T, S = batch.current_tokens, batch.current_sequences
         if capture and self.latent_buf is None:
@@ -295,6 +300,8 @@ class RaggedTransformer:
             ops.norm(resid, lw.norm1_g, xn, beta=lw.norm1_b, delta=pending, zero_delta=True,
                      res_out=resid if pending is not None else None, eps=s.norm_eps, layer_norm=ln)
             kv_layer = kv.get_cache(li)
+            if self._pending_restore is not None:
+                self._restore_step(li)  # deferred HCache restore: this layer's K/V must land before its attention
             ops.qkv_rope_kv_append(xn, lw.w_qkv, lw.b_qkv, self.qkv_buf[:T], self.q_buf[:T], kv_layer, pos, slot,
                                    self.inv_freq, self.n_q, self.n_kv, self.d, s.rot_dim, bs, workspace=self.ws_gemm)
             attn = self.attn_buf[:T]
@@ -311,6 +318,8 @@ class RaggedTransformer:
                 x2 = ops.norm(resid, lw.norm2_g, self.xn2[:T], beta=lw.norm2_b, delta=d1, zero_delta=True, res_out=resid,
                               eps=s.norm_eps, layer_norm=ln)
                 pending = self._mlp(x2, lw, T, force_accum=False)
+        if self._pending_restore is not None:
+            self.finish_pending_restore()
         # ---- last-token logits ----
         fin = self.xn2[:T]
         if s.final_norm:
@@ -319,11 +328,19 @@ class RaggedTransformer:
         else:
             ones = torch.ones(s.hidden, dtype=self.dtype, device=self.device)
             ops.norm(resid, ones, self.xn[:T], delta=pending, zero_delta=True, res_out=fin, eps=s.norm_eps)
-        hidden = ops.gather_rows(fin, batch.last_rows(), self.hidden_last[:S])
-        logits = ops.gemm(hidden, w.lm_head, self.logits_local[:S], bias=w.lm_head_b, workspace=self.ws_gemm)
+        if all_logits:
+            out_local = torch.empty((T, self.info.vocab), dtype=self.dtype, device=self.device)
+            logits = ops.gemm(fin, w.lm_head, out_local, bias=w.lm_head_b, workspace=self.ws_gemm)
+            n_rows = T
+        else:
+            hidden = ops.gather_rows(fin, batch.last_rows(), self.hidden_last[:S])
+            logits = ops.gemm(hidden, w.lm_head, self.logits_local[:S], bias=w.lm_head_b, workspace=self.ws_gemm)
+            n_rows = S
         if self.tp_size > 1:
             ranges = [shard_info(s, r, self.tp_size).vocab_range for r in range(self.tp_size)]
-            logits = self.comm.all_gather_logits(logits, self.logits_full[:S], ranges)
+            full = self.logits_full[:S] if not all_logits else torch.empty((n_rows, s.vocab), dtype=self.dtype,
+                                                                           device=self.device)
+            logits = self.comm.all_gather_logits(logits, full, ranges)
         return logits, (self.latent_buf[:, :T] if capture else None)
 
     # ------------------------------------------------------------------------------------------------
@@ -336,13 +353,18 @@ class RaggedTransformer:
         return lw.w_qkv[r0:], (lw.b_qkv[r0:] if lw.b_qkv is not None else None)
 
     def restore_kv(self, batch: RaggedBatchWrapper, latents: Sequence[torch.Tensor],
-                   layers: Optional[Sequence[int]] = None) -> None:
+                   layers: Optional[Sequence[int]] = None, defer: bool = False) -> None:
         """Rebuild the paged K/V of the batch's tokens from saved hidden states.
 
         ``latents``: one host tensor per sequence of the batch, ``[n_saved_layers, n_tokens_i, hidden]``, whose
         leading axis follows ``layers`` (default: every layer). Pinned tensors stream asynchronously; pageable
         ones go through the driver's staging path. Returns without waiting for the projections; kernels of the
         next ``put`` queue behind them on the same stream.
+
+        ``defer=True`` only starts the host-to-device stream; the projection of layer ``l`` is then issued by the
+        next ``forward`` immediately before its own layer ``l`` — the new turn's prefill fills the gaps in which
+        the compute stream would otherwise wait for PCIe (restore is IO-bound on B200), so time-to-first-token
+        approaches the pure transfer time.
         """
         s, ops = self.spec, self.ops
         layers = list(range(s.n_layers)) if layers is None else list(layers)
@@ -358,26 +380,73 @@ class RaggedTransformer:
                 wk, bk = self.kv_weight(li)
                 ops.restore_kv_proj(lat, wk, bk, kv.get_cache(li), pos, slot, self.inv_freq, self.n_kv, self.d, s.rot_dim, bs)
             return
+        self.finish_pending_restore()
         comp = torch.cuda.current_stream()
         io = self.io_stream
         io.wait_stream(comp)  # staging slots may still feed kernels of an earlier restore
+        # private copy of the per-token metadata: the batch wrapper's buffers are rewritten by the next forward
+        self.restore_pos[:T].copy_(pos, non_blocking=True)
+        self.restore_slot[:T].copy_(slot, non_blocking=True)
+        st = {"T": T, "layers": layers, "latents": list(latents), "issued": 0, "done": 0, "by_layer": {}}
         for i, li in enumerate(layers):
-            k = i % RESTORE_SLOTS
-            stage = self.restore_stage[k]
-            with torch.cuda.stream(io):
-                if i >= RESTORE_SLOTS:
-                    io.wait_event(self.ev_consumed[k])
-                off = 0
-                for lat in latents:
-                    n = int(lat.shape[1])
-                    stage[off:off + n].copy_(lat[i], non_blocking=True)
-                    off += n
-                self.ev_loaded[k].record(io)
-            comp.wait_event(self.ev_loaded[k])
-            wk, bk = self.kv_weight(li)
-            ops.restore_kv_proj(stage[:T], wk, bk, kv.get_cache(li), pos, slot, self.inv_freq, self.n_kv, self.d,
-                                s.rot_dim, bs, scratch=self.kv_scratch[:T] if self.kv_scratch is not None else None)
-            self.ev_consumed[k].record(comp)
+            st["by_layer"].setdefault(li, []).append(i)
+        self._pending_restore = st
+        for _ in range(min(RESTORE_SLOTS, len(layers))):
+            self._restore_issue_h2d(st)
+        if not defer:
+            self.finish_pending_restore()
+
+    def _restore_issue_h2d(self, st) -> None:
+        """Queue the H2D of the next saved layer into its staging slot (IO stream)."""
+        i = st["issued"]
+        k = i % RESTORE_SLOTS
+        io = self.io_stream
+        stage = self.restore_stage[k]
+        with torch.cuda.stream(io):
+            if i >= RESTORE_SLOTS:
+                io.wait_event(self.ev_consumed[k])
+            off = 0
+            for lat in st["latents"]:
+                n = int(lat.shape[1])
+                stage[off:off + n].copy_(lat[i], non_blocking=True)
+                off += n
+            self.ev_loaded[k].record(io)
+        st["issued"] = i + 1
+
+    def _restore_project(self, st, i: int) -> None:
+        """Project saved layer index ``i`` (compute stream) and keep the IO stream RESTORE_SLOTS layers ahead."""
+        s, kv = self.spec, self._state_manager
+        li = st["layers"][i]
+        k = i % RESTORE_SLOTS
+        T = st["T"]
+        comp = torch.cuda.current_stream()
+        comp.wait_event(self.ev_loaded[k])
+        wk, bk = self.kv_weight(li)
+        self.ops.restore_kv_proj(self.restore_stage[k][:T], wk, bk, kv.get_cache(li), self.restore_pos[:T],
+                                 self.restore_slot[:T], self.inv_freq, self.n_kv, self.d, s.rot_dim, kv.kv_block_size,
+                                 scratch=self.kv_scratch[:T] if self.kv_scratch is not None else None)
+        self.ev_consumed[k].record(comp)
+        st["done"] = i + 1
+        if st["issued"] < len(st["layers"]):
+            self._restore_issue_h2d(st)
+
+    def _restore_step(self, li: int) -> None:
+        """Called by ``forward`` right before layer ``li`` touches its KV cache."""
+        st = self._pending_restore
+        for i in st["by_layer"].get(li, ()):
+            while st["done"] <= i:  # saved layers are consumed in order
+                self._restore_project(st, st["done"])
+        if st["done"] >= len(st["layers"]):
+            self._pending_restore = None
+
+    def finish_pending_restore(self) -> None:
+        """Run whatever is left of a deferred restore now (compute stream)."""
+        st = self._pending_restore
+        if st is None:
+            return
+        while st["done"] < len(st["layers"]):
+            self._restore_project(st, st["done"])
+        self._pending_restore = None
 
     def restore_kv_pages(self, block_ids: torch.Tensor, kv_host: torch.Tensor, layers: Sequence[int]) -> None:
         """Plain KV reload for the layers the planner assigned to KV offload: ``kv_host`` is

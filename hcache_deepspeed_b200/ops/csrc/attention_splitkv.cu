@@ -18,8 +18,9 @@
 
 namespace hds {
 
-constexpr int kAttnThreads = 256;
-constexpr int kAttnTok = 128;  // KV tokens per pipeline stage
+constexpr int kAttnConsumerWarps = 8;
+constexpr int kAttnThreads = (kAttnConsumerWarps + 1) * 32;  // 8 consumer warps + 1 TMA producer warp
+constexpr int kAttnTok = 128;                                 // KV tokens per pipeline stage
 constexpr int kAttnStages = 3;
 
 struct AttnArgs {
@@ -42,34 +43,39 @@ __host__ __device__ constexpr size_t attn_stage_bytes() {
 }
 template <int D, int R>
 __host__ __device__ constexpr size_t attn_smem_bytes() {
-    return kAttnStages * attn_stage_bytes<D>() + static_cast<size_t>(R) * D * 4 /*q*/ +
-           2ull * R * kAttnTok * 4 /*partial scores*/ + static_cast<size_t>(R) * kAttnTok * 4 /*p*/ + 512 + 1024;
+    return kAttnStages * attn_stage_bytes<D>() + static_cast<size_t>(R) * D * 4 /*q*/ + 512 + 1024;
 }
 
+__device__ __forceinline__ float ex2f(float x) {
+    float y;
+    asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+    return y;
+}
+
+// Warp-independent formulation: consumer warp w owns tokens [16w, 16w+16) of every 128-token tile for BOTH
+// the q.K^T and the P.V step and keeps its own running (max, sum, accumulator); the eight partial states are
+// merged once at the end. Nothing in the main loop synchronises the CTA: warps wait on the stage's TMA
+// mbarrier and release the stage through a second mbarrier that the producer warp waits on.
 template <int D, int R, bool kBf16>
 __global__ void __launch_bounds__(kAttnThreads, 1)
 paged_attn_splitkv_kernel(const __grid_constant__ CUtensorMap tmap_kv, const AttnArgs a) {
     constexpr int PANELS = D / 64;                 // 128-byte column panels per row
     constexpr int PANEL_BYTES = kAttnTok * 128;    // one panel of a 128-token tile
     constexpr int TILE_BYTES = PANELS * PANEL_BYTES;
-    constexpr int CH_QK = D / 16;                  // 16-byte chunks per thread in the QK phase (2 threads/token)
-    constexpr int CV = D / 8;                      // chunks per V row
-    constexpr int NG = kAttnThreads / CV;          // token groups in the PV phase
+    constexpr int CH = D / 16;                     // 16-byte K chunks per lane (two lanes share a token)
+    constexpr int EPL = D / 32;                    // output dims per lane in the PV step
 
     extern __shared__ uint8_t smem_raw[];
     uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
     uint8_t* stages = smem;
-    float* q_s = reinterpret_cast<float*>(smem + kAttnStages * attn_stage_bytes<D>());
-    float* sc_s = q_s + R * D;                     // [2][R][128]
-    float* p_s = sc_s + 2 * R * kAttnTok;          // [R][128]
-    float* m_s = p_s + R * kAttnTok;               // [R]
-    float* l_s = m_s + R;                          // [R]
-    float* scale_s = l_s + R;                      // [R]
-    uint64_t* full_bar = reinterpret_cast<uint64_t*>(scale_s + R + 2);
-    full_bar = reinterpret_cast<uint64_t*>((reinterpret_cast<uintptr_t>(full_bar) + 7) & ~uintptr_t(7));
-    int* flag_s = reinterpret_cast<int*>(full_bar + kAttnStages);
+    float* q_s = reinterpret_cast<float*>(smem + kAttnStages * attn_stage_bytes<D>());  // [R][D], pre-scaled
+    uint64_t* full_bar = reinterpret_cast<uint64_t*>(q_s + R * D);
+    uint64_t* empty_bar = full_bar + kAttnStages;
+    int* flag_s = reinterpret_cast<int*>(empty_bar + kAttnStages);
+    float* ml_fin = reinterpret_cast<float*>(flag_s + 2);  // [R][2] merged (m, l) of this CTA
 
     const int tid = threadIdx.x;
+    const int warp = tid >> 5, lane = tid & 31;
     const int item_idx = blockIdx.x, kvh = blockIdx.y, split = blockIdx.z;
     const hds_attn_item item = a.items[item_idx];
     const int G = a.n_q_heads / a.n_kv_heads;
@@ -82,15 +88,15 @@ paged_attn_splitkv_kernel(const __grid_constant__ CUtensorMap tmap_kv, const Att
     const int t0 = split * tps;
     const int t1 = min(tiles_total, t0 + tps);
     const int bs = a.block_size;
-    const int bps = kAttnTok / bs;  // blocks per stage
-    const int32_t* table = a.block_tables + static_cast<int64_t>(item.seq) * a.max_blocks_per_seq;
 
     if (tid == 0) {
         prefetch_tmap(&tmap_kv);
-        for (int i = 0; i < kAttnStages; ++i) mbar_init(&full_bar[i], 1);
+        for (int i = 0; i < kAttnStages; ++i) {
+            mbar_init(&full_bar[i], 1);
+            mbar_init(&empty_bar[i], kAttnConsumerWarps);
+        }
         fence_barrier_init();
     }
-    // q -> shared (fp32, pre-scaled so that softmax is exp2)
     for (int e = tid; e < R * D; e += kAttnThreads) {
         const int r = e / D, dd = e % D;
         float v = 0.0f;
@@ -101,178 +107,194 @@ paged_attn_splitkv_kernel(const __grid_constant__ CUtensorMap tmap_kv, const Att
         }
         q_s[e] = v;
     }
-    if (tid < R) {
-        m_s[tid] = -INFINITY;
-        l_s[tid] = 0.0f;
-    }
     __syncthreads();
 
-    auto issue_tile = [&](int ti) {
-        const int stage = (ti - t0) % kAttnStages;
-        uint8_t* kdst = stages + stage * attn_stage_bytes<D>();
-        uint8_t* vdst = kdst + TILE_BYTES;
-        const int tok0 = ti * kAttnTok;
-        const int n_tok = min(kAttnTok, kv_len - tok0);
-        const int nb = (n_tok + bs - 1) / bs;
-        mbar_expect_tx(&full_bar[stage], static_cast<uint32_t>(nb) * bs * D * 2 * 2);
-        for (int b = 0; b < nb; ++b) {
-            const int blk = table[tok0 / bs + b];
-            const int krow = ((blk * 2 + 0) * a.n_kv_heads + kvh) * bs;
-            const int vrow = ((blk * 2 + 1) * a.n_kv_heads + kvh) * bs;
+    float m_run[R], l_run[R], acc[R][EPL];
 #pragma unroll
-            for (int p = 0; p < PANELS; ++p) {
-                tma_load_2d(kdst + p * PANEL_BYTES + b * bs * 128, &tmap_kv, &full_bar[stage], p * 64, krow,
-                            kEvictFirst);
-                tma_load_2d(vdst + p * PANEL_BYTES + b * bs * 128, &tmap_kv, &full_bar[stage], p * 64, vrow,
-                            kEvictFirst);
-            }
-        }
-    };
-    if (tid == 0) {
-        for (int ti = t0; ti < t1 && ti < t0 + kAttnStages; ++ti) issue_tile(ti);
+    for (int r = 0; r < R; ++r) {
+        m_run[r] = -INFINITY;
+        l_run[r] = 0.0f;
+#pragma unroll
+        for (int i = 0; i < EPL; ++i) acc[r][i] = 0.0f;
     }
 
-    float acc[R][8];
+    if (warp == kAttnConsumerWarps) {
+        // ===================== TMA producer =====================
+        if (lane == 0) {
+            const int32_t* table = a.block_tables + static_cast<int64_t>(item.seq) * a.max_blocks_per_seq;
+            uint32_t stage = 0, phase = 0;
+            for (int ti = t0; ti < t1; ++ti) {
+                mbar_wait(&empty_bar[stage], phase ^ 1);
+                uint8_t* kdst = stages + stage * attn_stage_bytes<D>();
+                uint8_t* vdst = kdst + TILE_BYTES;
+                const int tok0 = ti * kAttnTok;
+                const int n_tok = min(kAttnTok, kv_len - tok0);
+                const int nb = (n_tok + bs - 1) / bs;
+                mbar_expect_tx(&full_bar[stage], static_cast<uint32_t>(nb) * bs * D * 2 * 2);
+                for (int b = 0; b < nb; ++b) {
+                    const int blk = table[tok0 / bs + b];
+                    const int krow = ((blk * 2 + 0) * a.n_kv_heads + kvh) * bs;
+                    const int vrow = ((blk * 2 + 1) * a.n_kv_heads + kvh) * bs;
 #pragma unroll
-    for (int r = 0; r < R; ++r)
+                    for (int p = 0; p < PANELS; ++p) {
+                        tma_load_2d(kdst + p * PANEL_BYTES + b * bs * 128, &tmap_kv, &full_bar[stage], p * 64, krow,
+                                    kEvictFirst);
+                        tma_load_2d(vdst + p * PANEL_BYTES + b * bs * 128, &tmap_kv, &full_bar[stage], p * 64, vrow,
+                                    kEvictFirst);
+                    }
+                }
+                if (++stage == kAttnStages) {
+                    stage = 0;
+                    phase ^= 1;
+                }
+            }
+        }
+    } else {
+        // ===================== consumers =====================
+        const int j = lane & 15, hh = lane >> 4;   // token slot inside the warp's 16-token strip, dim half
+        const int rt = warp * 16 + j;              // row of this lane's token inside the tile
+        float qreg[R == 1 ? CH * 8 : 1];
+        if (R == 1) {
 #pragma unroll
-        for (int i = 0; i < 8; ++i) acc[r][i] = 0.0f;
-
-    const int warp = tid >> 5, lane = tid & 31;
-    for (int ti = t0; ti < t1; ++ti) {
-        const int it = ti - t0;
-        const int stage = it % kAttnStages;
-        const uint32_t phase = (it / kAttnStages) & 1;
-        const uint8_t* ktile = stages + stage * attn_stage_bytes<D>();
-        const uint8_t* vtile = ktile + TILE_BYTES;
-        const int tok0 = ti * kAttnTok;
-        const int n_tok = min(kAttnTok, kv_len - tok0);
-        mbar_wait(&full_bar[stage], phase);
-
-        // ---- S = q . K^T : thread (j, hh) covers half of token j's head dimension ----
-        {
-            const int j = tid & (kAttnTok - 1), hh = tid >> 7;
-            float part[R];
+            for (int i = 0; i < CH * 8; ++i) qreg[i] = q_s[hh * CH * 8 + i];
+        }
+        uint32_t stage = 0, phase = 0;
+        for (int ti = t0; ti < t1; ++ti) {
+            const uint8_t* ktile = stages + stage * attn_stage_bytes<D>();
+            const uint8_t* vtile = ktile + TILE_BYTES;
+            const int tok0 = ti * kAttnTok;
+            const int n_tok = min(kAttnTok, kv_len - tok0);
+            const int n_mine = min(16, max(0, n_tok - warp * 16));  // valid tokens of this warp's strip (uniform)
+            mbar_wait(&full_bar[stage], phase);
+            if (n_mine > 0) {
+                // ---- s = q . k for my token (half of the head dim per lane, combined by one shuffle) ----
+                float part[R];
 #pragma unroll
-            for (int r = 0; r < R; ++r) part[r] = 0.0f;
-            if (j < n_tok) {
+                for (int r = 0; r < R; ++r) part[r] = 0.0f;
+                if (j < n_mine) {
 #pragma unroll
-                for (int c = 0; c < CH_QK; ++c) {
-                    const int cg = hh * CH_QK + c;
-                    const int panel = cg >> 3, cc = cg & 7;
-                    const uint4 kk = *reinterpret_cast<const uint4*>(ktile + panel * PANEL_BYTES + j * 128 +
-                                                                    ((cc ^ (j & 7)) << 4));
-                    const float k0 = unpack_lo<kBf16>(kk.x), k1 = unpack_hi<kBf16>(kk.x);
-                    const float k2 = unpack_lo<kBf16>(kk.y), k3 = unpack_hi<kBf16>(kk.y);
-                    const float k4 = unpack_lo<kBf16>(kk.z), k5 = unpack_hi<kBf16>(kk.z);
-                    const float k6 = unpack_lo<kBf16>(kk.w), k7 = unpack_hi<kBf16>(kk.w);
+                    for (int c = 0; c < CH; ++c) {
+                        const int cg = hh * CH + c;
+                        const int panel = cg >> 3, cc = cg & 7;
+                        const uint4 kk = *reinterpret_cast<const uint4*>(ktile + panel * PANEL_BYTES + rt * 128 +
+                                                                        ((cc ^ (rt & 7)) << 4));
+                        float kf[8] = {unpack_lo<kBf16>(kk.x), unpack_hi<kBf16>(kk.x), unpack_lo<kBf16>(kk.y),
+                                       unpack_hi<kBf16>(kk.y), unpack_lo<kBf16>(kk.z), unpack_hi<kBf16>(kk.z),
+                                       unpack_lo<kBf16>(kk.w), unpack_hi<kBf16>(kk.w)};
+                        if (R == 1) {
+#pragma unroll
+                            for (int i = 0; i < 8; ++i) part[0] = fmaf(qreg[c * 8 + i], kf[i], part[0]);
+                        } else {
+#pragma unroll
+                            for (int r = 0; r < R; ++r) {
+                                const float4 qa = *reinterpret_cast<const float4*>(q_s + r * D + cg * 8);
+                                const float4 qb = *reinterpret_cast<const float4*>(q_s + r * D + cg * 8 + 4);
+                                part[r] += qa.x * kf[0] + qa.y * kf[1] + qa.z * kf[2] + qa.w * kf[3] + qb.x * kf[4] +
+                                           qb.y * kf[5] + qb.z * kf[6] + qb.w * kf[7];
+                            }
+                        }
+                    }
+                }
+                float p[R];
+#pragma unroll
+                for (int r = 0; r < R; ++r) {
+                    float sc = part[r] + __shfl_xor_sync(0xffffffffu, part[r], 16);
+                    const int q_pos = item.pos0 + r / G;
+                    const bool ok = (j < n_mine) && (tok0 + rt <= q_pos) && (r < rows);
+                    sc = ok ? sc : -INFINITY;
+                    float mx = sc;
+#pragma unroll
+                    for (int o = 8; o > 0; o >>= 1) mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, o));
+                    const float m_new = fmaxf(m_run[r], mx);
+                    const float scale = (m_run[r] == -INFINITY) ? 0.0f : ex2f(m_run[r] - m_new);
+                    const float pv = (m_new == -INFINITY) ? 0.0f : ex2f(sc - m_new);
+                    float ps = pv;
+#pragma unroll
+                    for (int o = 8; o > 0; o >>= 1) ps += __shfl_xor_sync(0xffffffffu, ps, o);
+                    l_run[r] = l_run[r] * scale + ps;
+                    m_run[r] = m_new;
+                    p[r] = pv;
+#pragma unroll
+                    for (int i = 0; i < EPL; ++i) acc[r][i] *= scale;
+                }
+                // ---- acc += p_j * v_j : every lane owns EPL output dims, tokens of the strip in turn ----
+                const int boff = lane * EPL * 2;                      // logical byte offset inside the V row
+                const int vpanel = boff >> 7, vcc = (boff & 127) >> 4, vin = boff & 15;
+                for (int jj = 0; jj < n_mine; ++jj) {
+                    const int rv = warp * 16 + jj;
+                    const uint8_t* vp = vtile + vpanel * PANEL_BYTES + rv * 128 + ((vcc ^ (rv & 7)) << 4) + vin;
+                    float vf[EPL];
+                    if (EPL == 4) {
+                        const uint2 vv = *reinterpret_cast<const uint2*>(vp);
+                        vf[0] = unpack_lo<kBf16>(vv.x); vf[1] = unpack_hi<kBf16>(vv.x);
+                        vf[2 % EPL] = unpack_lo<kBf16>(vv.y); vf[3 % EPL] = unpack_hi<kBf16>(vv.y);
+                    } else {
+                        const uint32_t vv = *reinterpret_cast<const uint32_t*>(vp);
+                        vf[0] = unpack_lo<kBf16>(vv); vf[1] = unpack_hi<kBf16>(vv);
+                    }
 #pragma unroll
                     for (int r = 0; r < R; ++r) {
-                        const float4 qa = *reinterpret_cast<const float4*>(q_s + r * D + cg * 8);
-                        const float4 qb = *reinterpret_cast<const float4*>(q_s + r * D + cg * 8 + 4);
-                        part[r] += qa.x * k0 + qa.y * k1 + qa.z * k2 + qa.w * k3 + qb.x * k4 + qb.y * k5 + qb.z * k6 +
-                                   qb.w * k7;
+                        const float pj = __shfl_sync(0xffffffffu, p[r], jj);
+#pragma unroll
+                        for (int i = 0; i < EPL; ++i) acc[r][i] = fmaf(pj, vf[i], acc[r][i]);
                     }
                 }
             }
-#pragma unroll
-            for (int r = 0; r < R; ++r) sc_s[(hh * R + r) * kAttnTok + j] = part[r];
-        }
-        __syncthreads();
-        // every thread is past the previous tile's PV: its stage can be refilled
-        if (tid == 0 && it >= 1 && ti - 1 + kAttnStages < t1) issue_tile(ti - 1 + kAttnStages);
-
-        // ---- online softmax: warp r owns query row r ----
-        if (warp < R && warp < rows) {
-            const int r = warp;
-            const int q_pos = item.pos0 + r / G;
-            float s[4];
-            float tmax = -INFINITY;
-#pragma unroll
-            for (int i = 0; i < 4; ++i) {
-                const int j = lane + 32 * i;
-                const bool ok = j < n_tok && (tok0 + j) <= q_pos;
-                s[i] = ok ? sc_s[r * kAttnTok + j] + sc_s[(R + r) * kAttnTok + j] : -INFINITY;
-                tmax = fmaxf(tmax, s[i]);
-            }
-            tmax = warp_max(tmax);
-            const float m_old = m_s[r];
-            const float m_new = fmaxf(m_old, tmax);
-            float psum = 0.0f;
-#pragma unroll
-            for (int i = 0; i < 4; ++i) {
-                const float p = (m_new == -INFINITY) ? 0.0f : exp2f(s[i] - m_new);
-                p_s[r * kAttnTok + lane + 32 * i] = p;
-                psum += p;
-            }
-            psum = warp_sum(psum);
-            if (lane == 0) {
-                const float sc = (m_old == -INFINITY) ? 0.0f : exp2f(m_old - m_new);
-                scale_s[r] = sc;
-                m_s[r] = m_new;
-                l_s[r] = l_s[r] * sc + psum;
-            }
-        }
-        __syncthreads();
-
-        // ---- O += P . V : thread (cv, g) owns 8 output dims for every NG-th token ----
-        {
-            const int cv = tid % CV, g = tid / CV;
-            const int panel = cv >> 3, cc = cv & 7;
-#pragma unroll
-            for (int r = 0; r < R; ++r) {
-                const float sc = scale_s[r];
-#pragma unroll
-                for (int i = 0; i < 8; ++i) acc[r][i] *= sc;
-            }
-            for (int j = g; j < n_tok; j += NG) {
-                const uint4 vv =
-                    *reinterpret_cast<const uint4*>(vtile + panel * PANEL_BYTES + j * 128 + ((cc ^ (j & 7)) << 4));
-                const float v0 = unpack_lo<kBf16>(vv.x), v1 = unpack_hi<kBf16>(vv.x);
-                const float v2 = unpack_lo<kBf16>(vv.y), v3 = unpack_hi<kBf16>(vv.y);
-                const float v4 = unpack_lo<kBf16>(vv.z), v5 = unpack_hi<kBf16>(vv.z);
-                const float v6 = unpack_lo<kBf16>(vv.w), v7 = unpack_hi<kBf16>(vv.w);
-#pragma unroll
-                for (int r = 0; r < R; ++r) {
-                    const float p = p_s[r * kAttnTok + j];
-                    acc[r][0] += p * v0; acc[r][1] += p * v1; acc[r][2] += p * v2; acc[r][3] += p * v3;
-                    acc[r][4] += p * v4; acc[r][5] += p * v5; acc[r][6] += p * v6; acc[r][7] += p * v7;
-                }
+            __syncwarp();
+            if (lane == 0) mbar_arrive(&empty_bar[stage]);
+            if (++stage == kAttnStages) {
+                stage = 0;
+                phase ^= 1;
             }
         }
     }
-    __syncthreads();  // all PV reads of the ring are done; reuse it for the cross-group reduction
+    __syncthreads();  // every consumer is done with the ring: reuse it to merge the eight warp states
 
-    // ---- reduce the NG partial accumulators through shared memory ----
-    float* red = reinterpret_cast<float*>(stages);  // [NG][R][D]
-    {
-        const int cv = tid % CV, g = tid / CV;
+    float* mg_ml = reinterpret_cast<float*>(stages);                       // [warps][R][2]
+    float* mg_o = mg_ml + kAttnConsumerWarps * R * 2;                      // [warps][R][D]
+    if (warp < kAttnConsumerWarps) {
 #pragma unroll
         for (int r = 0; r < R; ++r) {
-            float4* dst = reinterpret_cast<float4*>(red + (g * R + r) * D + cv * 8);
-            dst[0] = make_float4(acc[r][0], acc[r][1], acc[r][2], acc[r][3]);
-            dst[1] = make_float4(acc[r][4], acc[r][5], acc[r][6], acc[r][7]);
+            if (lane == 0) {
+                mg_ml[(warp * R + r) * 2 + 0] = m_run[r];
+                mg_ml[(warp * R + r) * 2 + 1] = l_run[r];
+            }
+#pragma unroll
+            for (int i = 0; i < EPL; ++i) mg_o[(warp * R + r) * D + lane * EPL + i] = acc[r][i];
         }
     }
     __syncthreads();
     const int64_t ws_base = (static_cast<int64_t>(item_idx) * a.n_kv_heads + kvh) * a.n_splits;
     for (int e = tid; e < rows * D; e += kAttnThreads) {
         const int r = e / D, dd = e % D;
-        float o = 0.0f;
-#pragma unroll 4
-        for (int g = 0; g < NG; ++g) o += red[(g * R + r) * D + dd];
+        float mx = -INFINITY;
+#pragma unroll
+        for (int w = 0; w < kAttnConsumerWarps; ++w) mx = fmaxf(mx, mg_ml[(w * R + r) * 2]);
+        float o = 0.0f, l = 0.0f;
+#pragma unroll
+        for (int w = 0; w < kAttnConsumerWarps; ++w) {
+            const float mw = mg_ml[(w * R + r) * 2];
+            const float wt = (mw == -INFINITY) ? 0.0f : ex2f(mw - mx);
+            l = fmaf(wt, mg_ml[(w * R + r) * 2 + 1], l);
+            o = fmaf(wt, mg_o[(w * R + r) * D + dd], o);
+        }
+        if (dd == 0) {
+            ml_fin[r * 2 + 0] = mx;
+            ml_fin[r * 2 + 1] = l;
+        }
         if (eff_splits == 1) {
             const int qi = r / G, gg = r % G;
             store_scalar<kBf16>(a.out, (static_cast<int64_t>(item.q_row0 + qi) * a.n_q_heads + kvh * G + gg) * D + dd,
-                                o / l_s[r]);
+                                o / l);
         } else {
             a.ws_o[((ws_base + split) * R + r) * D + dd] = o;
         }
     }
     if (eff_splits == 1) return;
+    __syncthreads();
     if (tid < rows) {
-        a.ws_ml[((ws_base + split) * R + tid) * 2 + 0] = m_s[tid];
-        a.ws_ml[((ws_base + split) * R + tid) * 2 + 1] = l_s[tid];
+        a.ws_ml[((ws_base + split) * R + tid) * 2 + 0] = ml_fin[tid * 2 + 0];
+        a.ws_ml[((ws_base + split) * R + tid) * 2 + 1] = ml_fin[tid * 2 + 1];
     }
     __threadfence();
     __syncthreads();
@@ -291,7 +313,7 @@ paged_attn_splitkv_kernel(const __grid_constant__ CUtensorMap tmap_kv, const Att
         float o = 0.0f, l = 0.0f;
         for (int s = 0; s < eff_splits; ++s) {
             const float ms = __ldcg(&a.ws_ml[((ws_base + s) * R + r) * 2]);
-            const float w = (ms == -INFINITY) ? 0.0f : exp2f(ms - mx);
+            const float w = (ms == -INFINITY) ? 0.0f : ex2f(ms - mx);
             l += w * __ldcg(&a.ws_ml[((ws_base + s) * R + r) * 2 + 1]);
             o += w * __ldcg(&a.ws_o[((ws_base + s) * R + r) * D + dd]);
         }

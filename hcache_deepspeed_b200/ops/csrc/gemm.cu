@@ -5,19 +5,19 @@
 
 namespace hds {
 
-template <int BN, int EPI, bool kBf16, int HD = 128>
+template <int BN, int EPI, bool kBf16, int HD = 128, int AM = 128>
 static int launch_gemm_inst(const CUtensorMap& ta, const CUtensorMap& tw, const GemmArgs& args, int grid,
                             cudaStream_t stream) {
-    auto kern = gemm_tn_kernel<BN, EPI, kBf16, HD>;
+    auto kern = gemm_tn_kernel<BN, EPI, kBf16, HD, AM>;
     static bool configured[64] = {false};
     int dev = 0;
     cudaGetDevice(&dev);
     if (!configured[dev & 63]) {
         HDS_CHECK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                            static_cast<int>(gemm_smem_bytes(BN))));
+                                            static_cast<int>(gemm_smem_bytes(BN, AM))));
         configured[dev & 63] = true;
     }
-    kern<<<grid, kGemmThreads, gemm_smem_bytes(BN), stream>>>(ta, tw, args);
+    kern<<<grid, kGemmThreads, gemm_smem_bytes(BN, AM), stream>>>(ta, tw, args);
     HDS_CHECK_CUDA(cudaGetLastError());
     return HDS_OK;
 }
@@ -38,6 +38,15 @@ static int launch_gemm_rope(int bn, int hd, const CUtensorMap& ta, const CUtenso
 template <int EPI, bool kBf16>
 static int launch_gemm_bn(int bn, const CUtensorMap& ta, const CUtensorMap& tw, const GemmArgs& args, int grid,
                           cudaStream_t stream) {
+    // decode-size M: compact A stages (16 or 64 rows) and a deeper weight pipeline
+    if (args.M <= 64 && (bn == 64 || bn == 128)) {
+        if (args.M <= 16) {
+            return bn == 64 ? launch_gemm_inst<64, EPI, kBf16, 128, 16>(ta, tw, args, grid, stream)
+                            : launch_gemm_inst<128, EPI, kBf16, 128, 16>(ta, tw, args, grid, stream);
+        }
+        return bn == 64 ? launch_gemm_inst<64, EPI, kBf16, 128, 64>(ta, tw, args, grid, stream)
+                        : launch_gemm_inst<128, EPI, kBf16, 128, 64>(ta, tw, args, grid, stream);
+    }
     {
         switch (bn) {
             case 32: return launch_gemm_inst<32, EPI, kBf16>(ta, tw, args, grid, stream);

@@ -32,15 +32,21 @@ constexpr int kGemmBK = 64;
 constexpr int kGemmThreads = 192;
 constexpr int kMaxPeers = 8;
 
-__host__ __device__ constexpr int gemm_stages(int bn) {
-    // (16 KB A + bn*128 B W) per stage, ~196 KB of the 227 KB budget
-    return bn >= 256 ? 4 : bn >= 128 ? 6 : bn >= 64 ? 8 : 10;
+// Pipeline depth: as many (A, W) stages as fit in ~200 KB, at most 16. `am` is the number of A rows kept in
+// shared memory: 128 normally; 16 / 64 for decode-size M, where the TMA box only delivers the live rows and
+// the tensor core reads the remaining rows of its 128-row operand from whatever follows in shared memory
+// (those rows only feed accumulator rows that are never stored). Shrinking A leaves room for 2x the weight
+// bytes in flight, which is what a weight-streaming GEMM needs to cover HBM latency.
+__host__ __device__ constexpr int gemm_stages(int bn, int am = 128) {
+    return (200 * 1024) / (am * 128 + bn * 128) > 16 ? 16 : (200 * 1024) / (am * 128 + bn * 128);
 }
 __host__ __device__ constexpr uint32_t gemm_tmem_cols(int bn) {
     return 2 * bn <= 32 ? 32 : 2 * bn <= 64 ? 64 : 2 * bn <= 128 ? 128 : 2 * bn <= 256 ? 256 : 512;
 }
-__host__ __device__ constexpr size_t gemm_smem_bytes(int bn) {
-    return static_cast<size_t>(gemm_stages(bn)) * (kGemmBM * kGemmBK * 2 + bn * kGemmBK * 2) + 256 + 1024;
+__host__ __device__ constexpr size_t gemm_smem_bytes(int bn, int am = 128) {
+    // stages + barriers (2*stages + 4 mbarriers, TMEM slot) + 1 KB alignment slack; with am < 128 the last A
+    // stage is read 16 KB deep, which stays inside the W region that follows (>= 16 KB for every config used)
+    return static_cast<size_t>(gemm_stages(bn, am)) * (am * kGemmBK * 2 + bn * kGemmBK * 2) + 512 + 1024;
 }
 
 struct GemmArgs {
@@ -341,12 +347,14 @@ __device__ __forceinline__ void epilogue_kv_rope(const GemmArgs& a, uint32_t tad
 // ---------------------------------------------------------------------------------------------
 // The kernel
 // ---------------------------------------------------------------------------------------------
-template <int BN, int EPI, bool kBf16, int HD = 128>
+template <int BN, int EPI, bool kBf16, int HD = 128, int AM = 128>
 __global__ void __launch_bounds__(kGemmThreads, 1)
 gemm_tn_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_w,
                const GemmArgs args) {
-    constexpr int STAGES = gemm_stages(BN);
-    constexpr uint32_t A_BYTES = kGemmBM * kGemmBK * 2;
+    constexpr int STAGES = gemm_stages(BN, AM);
+    constexpr uint32_t A_BYTES = AM * kGemmBK * 2;
+    static_assert(AM == 128 || static_cast<uint32_t>(STAGES) * BN * kGemmBK * 2 >= 16384,
+                  "compact-A configs need >= 16 KB of W stages behind the A stages");
     constexpr uint32_t W_BYTES = BN * kGemmBK * 2;
     constexpr uint32_t TMEM_COLS = gemm_tmem_cols(BN);
     constexpr uint32_t IDESC = make_idesc_f16(kGemmBM, BN, kBf16, false, false);
