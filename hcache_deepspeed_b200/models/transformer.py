@@ -54,15 +54,26 @@ class TPComm:
             dist.all_reduce(delta32, group=self.group)
 
     def all_gather_logits(self, local: torch.Tensor, out_full: torch.Tensor, vocab_ranges) -> torch.Tensor:
+        """Vocabulary-sharded logits -> full ``[n, vocab]`` on every rank (ref: llama_v2/model.py:195-197).
+        Uneven vocabulary shards are padded to the widest one for the collective."""
         import torch.distributed as dist
-        if all((b - a) == (vocab_ranges[0][1] - vocab_ranges[0][0]) for a, b in vocab_ranges):
-            parts = torch.empty((self.size, ) + tuple(local.shape), dtype=local.dtype, device=local.device)
-            dist.all_gather_into_tensor(parts, local.contiguous(), group=self.group)
-            out_full.copy_(parts.permute(1, 0, 2).reshape(local.shape[0], -1))
+        widths = [b - a for a, b in vocab_ranges]
+        wmax = max(widths)
+        n = local.shape[0]
+        src = local
+        if local.shape[1] != wmax:
+            src = torch.zeros((n, wmax), dtype=local.dtype, device=local.device)
+            src[:, :local.shape[1]] = local
+        parts = torch.empty((self.size, n, wmax), dtype=local.dtype, device=local.device)
+        if local.device.type == "cuda":
+            dist.all_gather_into_tensor(parts, src.contiguous(), group=self.group)
+        else:  # gloo wants a list of per-rank outputs
+            dist.all_gather(list(parts.unbind(0)), src.contiguous(), group=self.group)
+        if all(w == wmax for w in widths):
+            out_full.copy_(parts.permute(1, 0, 2).reshape(n, -1))
         else:
-            parts = [torch.empty((local.shape[0], b - a), dtype=local.dtype, device=local.device) for a, b in vocab_ranges]
-            dist.all_gather(parts, local.contiguous(), group=self.group)
-            out_full.copy_(torch.cat(parts, dim=1))
+            for r, (a, b) in enumerate(vocab_ranges):
+                out_full[:, a:b] = parts[r, :, :b - a]
         return out_full
 
 
@@ -135,7 +146,14 @@ class RaggedTransformer:
         self.q_buf = buf(T, self.n_q * self.d)
         self.attn_buf = buf(T, self.n_q * self.d)
         self.act_buf = buf(T, inter)
-        self.delta32 = buf(T, H, dtype=torch.float32)
+        # fp32 pending-delta buffers; two alternate under tensor parallelism (symmetric memory when fused) so a
+        # fast rank's next reducing GEMM never lands in a buffer a slow rank is still consuming
+        if self.tp_size > 1 and getattr(self.comm, "fused", False):
+            self._delta_bufs = self.comm.alloc_delta(T, H, 2)
+        else:
+            self._delta_bufs = [buf(T, H, dtype=torch.float32) for _ in range(2 if self.tp_size > 1 else 1)]
+        self._delta_idx = 0
+        self.delta32 = self._delta_bufs[0]
         self.delta16 = buf(T, H)
         self.hidden_last = buf(S, H)
         self.logits_local = buf(S, self.info.vocab)
@@ -223,10 +241,12 @@ class RaggedTransformer:
                       last_into_delta: bool = True) -> torch.Tensor:
         """y = x @ w.T (+b), left as the pending delta. fp32 partial sums when the GEMM is split over K or ranks."""
         if force_accum or T <= ACCUM_MAX_TOKENS or self.tp_size > 1:
-            d32 = self.delta32[:T]
+            d32 = self._delta_bufs[self._delta_idx][:T]
             self.ops.gemm_accum(x, w, d32, bias=b, comm=self.comm)
-            if self.tp_size > 1 and last_into_delta:
-                self.comm.all_reduce_delta(d32)
+            if last_into_delta:  # this delta is complete: the next reducing GEMM uses the other buffer
+                if self.tp_size > 1:
+                    self.comm.all_reduce_delta(d32)
+                self._delta_idx = (self._delta_idx + 1) % len(self._delta_bufs)
             return d32
         return self.ops.gemm(x, w, self.delta16[:T], bias=b)
 
@@ -245,7 +265,7 @@ class RaggedTransformer:
         accumulate straight into the fp32 pending delta scaled by their gate weight.
         Ref: modules/implementations/moe/cutlass_multi_gemm.py:28-249, ragged_ops/top_k_gating."""
         s = self.spec
-        d32 = self.delta32[:T]
+        d32 = self._delta_bufs[self._delta_idx][:T]
         scores = ref.gemm(x, lw.w_router, out_dtype=torch.float32) if self.device.type == "cpu" else \
             self.ops.k.gemm(x, lw.w_router).float()
         probs = torch.softmax(scores, dim=-1)
@@ -274,7 +294,12 @@ class RaggedTransformer:
             g = torch.sigmoid(ref.gemm(x, lw.w_shared_gate, out_dtype=torch.float32))
             d32 += ys.float() * g
         if self.tp_size > 1:
-            self.comm.all_reduce_delta(d32)
+            if getattr(self.comm, "fused", False):
+                import torch.distributed as dist
+                dist.all_reduce(d32, group=self.comm.group)  # MoE partials are added locally: plain all-reduce
+            else:
+                self.comm.all_reduce_delta(d32)
+        self._delta_idx = (self._delta_idx + 1) % len(self._delta_bufs)
         return d32
 
     def forward(self, batch: RaggedBatchWrapper, capture: bool = False,

@@ -46,7 +46,7 @@ def test_restore_equals_live_kv_llama7b_shapes():
     _, l2 = eng.put([1], [p2])  # second chunk of the same sequence
     saved = torch.cat([l1[0], l2[0]], dim=1)
     assert saved.shape == (2, 745, spec.hidden) and l1[0].is_pinned()
-    eng.restore_kv([9], [torch.cat([p1, p2])], [saved])
+    eng.restore_kv([9], [torch.cat([p1, p2])], [saved], defer=False)  # the test reads the pages directly
     kv = eng.state_manager.kv_cache.full_cache
     s1, s9 = eng.state_manager.get_sequence(1), eng.state_manager.get_sequence(9)
     assert s9.seen_tokens == 745
@@ -58,6 +58,29 @@ def test_restore_equals_live_kv_llama7b_shapes():
     la, _ = eng.put([1], [probe], capture_latents=False)
     lb, _ = eng.put([9], [probe], capture_latents=False)
     torch.testing.assert_close(la.float(), lb.float(), rtol=3e-2, atol=3e-2)
+
+
+def test_deferred_restore_overlaps_next_put():
+    """restore_kv(defer=True) + put == restore_kv(defer=False) + put, for one and for two sessions per call."""
+    from hcache_deepspeed_b200.inference.v2 import build_engine_from_arch
+    from hcache_deepspeed_b200.models.arch import named_arch
+    spec = named_arch("llama-2-7b").scaled(n_layers=3)
+    eng = build_engine_from_arch(spec, _cfg(T=1024, ctx=2048, mem=1 << 30), seed=4, device=torch.device("cuda"))
+    g = torch.Generator().manual_seed(0)
+    pa, pb = torch.randint(0, spec.vocab, (500, ), generator=g), torch.randint(0, spec.vocab, (130, ), generator=g)
+    _, lat = eng.put([1, 2], [pa, pb])
+    turn = [torch.randint(0, spec.vocab, (40, ), generator=g), torch.randint(0, spec.vocab, (3, ), generator=g)]
+    eng.restore_kv([10, 11], [pa, pb], lat, defer=False)
+    want, _ = eng.put([10, 11], turn, capture_latents=False)
+    eng.restore_kv([20, 21], [pa, pb], lat, defer=True)
+    got, _ = eng.put([20, 21], turn, capture_latents=False)
+    torch.testing.assert_close(got.float(), want.float(), rtol=0, atol=0)
+    live, _ = eng.put([1, 2], turn, capture_latents=False)
+    torch.testing.assert_close(got.float(), live.float(), rtol=3e-2, atol=3e-2)
+    # a deferred restore that is never followed by a forward is completed by flush
+    eng.restore_kv([30], [pa], [lat[0]], defer=True)
+    eng.flush(30)
+    torch.cuda.synchronize()
 
 
 def test_async_capture_and_flush():
