@@ -1,4 +1,5 @@
 // Launchers for the tcgen05 GEMM family (see gemm_core.cuh for the kernel).
+#include <stdlib.h>
 #include "gemm_core.cuh"
 #include "hds_host.cuh"
 #include "../../../include/hds_b200.h"
@@ -114,10 +115,14 @@ struct Operands {
 static int prepare(GemmArgs& g, Operands& ops, const void* A, int64_t lda, const void* W, int64_t ldw, int M, int N,
                    int K, bool bf16, int bn, int splits) {
     HDS_REQUIRE(M > 0 && N > 0 && K > 0, "gemm: empty problem");
-    HDS_REQUIRE(K % 8 == 0 && lda % 8 == 0 && ldw % 8 == 0, "gemm: K, lda, ldw must be multiples of 8 elements");
+    HDS_REQUIRE(K % 8 == 0 && lda % 8 == 0 && (ldw < 0 || ldw % 8 == 0),
+                "gemm: K, lda, ldw must be multiples of 8 elements");
+    HDS_REQUIRE(ldw >= 0 || bn >= 32, "gemm: tiled weights need a tile width >= 32");
     g.M = M;
     g.N = N;
     g.K = K;
+    static const int debug_skip = getenv("HDS_GEMM_DEBUG") ? atoi(getenv("HDS_GEMM_DEBUG")) : 0;
+    g.debug_skip = debug_skip;
     const int kb_total = (K + kGemmBK - 1) / kGemmBK;
     if (splits < 1) splits = 1;
     if (splits > kb_total) splits = kb_total;
@@ -133,8 +138,17 @@ static int prepare(GemmArgs& g, Operands& ops, const void* A, int64_t lda, const
     int rc = make_tmap_2d_16b(&ops.ta, A, static_cast<uint64_t>(K), static_cast<uint64_t>(M),
                               static_cast<uint64_t>(lda) * 2, kGemmBK, box_rows, bf16);
     if (rc) return rc;
-    rc = make_tmap_2d_16b(&ops.tw, W, static_cast<uint64_t>(K), static_cast<uint64_t>(N),
-                          static_cast<uint64_t>(ldw) * 2, kGemmBK, bn, bf16);
+    if (ldw < 0) {
+        // pre-tiled weights: [ceil(N/32)][ceil(K/64)][32][64] — one TMA instruction per k-block fetches BN/32
+        // contiguous 4 KB chunks (one per 32-row strip)
+        g.w_tiled = 1;
+        const uint64_t strips = (static_cast<uint64_t>(N) + 31) / 32;
+        rc = make_tmap_3d_16b(&ops.tw, W, 64, static_cast<uint64_t>(kb_total) * 32, strips, 128,
+                              static_cast<uint64_t>(kb_total) * 4096, 64, 32, static_cast<uint32_t>(bn / 32), bf16);
+    } else {
+        rc = make_tmap_2d_16b(&ops.tw, W, static_cast<uint64_t>(K), static_cast<uint64_t>(N),
+                              static_cast<uint64_t>(ldw) * 2, kGemmBK, bn, bf16);
+    }
     return rc;
 }
 

@@ -54,6 +54,8 @@ struct GemmArgs {
     int splits;            // split-K factor (>=1, no empty split)
     int kb_per_split;      // k-blocks (of 64) per split
     uint32_t a_tx_bytes;   // bytes delivered by one A box (box rows * 128)
+    int debug_skip;        // experiments only (HDS_GEMM_DEBUG): bit0 = no A loads, bit1 = no MMA issue (results invalid)
+    int w_tiled;           // W is stored pre-tiled [N/32][K/64][32][64]: every TMA box is one contiguous 4 KB chunk
     int act;               // Activation
     // EPI_STORE / EPI_GATED
     void* out;
@@ -411,14 +413,26 @@ gemm_tn_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
                 const int sp = rest / n_tiles;
                 const int kb0 = sp * args.kb_per_split;
                 const int kb1 = min(kb_total, kb0 + args.kb_per_split);
-                for (int kb = kb0; kb < kb1; ++kb) {
+                // Single m-tile (decode): every CTA needs the SAME activation k-block at the same moment, i.e. 148
+                // requests for a handful of L2 lines per step — the lines' L2 slices serialise them (~0.3 us per
+                // k-block, independent of tile size or pipeline depth). Starting each CTA at a different k offset
+                // spreads the requests over all slices; summation order is irrelevant to the accumulator.
+                const int nkb = kb1 - kb0;
+                const int rot = (m_tiles == 1) ? static_cast<int>((blockIdx.x * 5u) % static_cast<unsigned>(nkb)) : 0;
+                for (int it = 0; it < nkb; ++it) {
+                    const int kb = kb0 + (it + rot < nkb ? it + rot : it + rot - nkb);
                     mbar_wait(&empty_bar[stage], phase ^ 1);
-                    mbar_expect_tx(&full_bar[stage], args.a_tx_bytes + W_BYTES);
+                    mbar_expect_tx(&full_bar[stage], ((args.debug_skip & 1) ? 0u : args.a_tx_bytes) + W_BYTES);
                     // activations are re-read by every n-tile: keep them in L2; weights stream once per m-wave
-                    tma_load_2d(smem_a + stage * A_BYTES, &tmap_a, &full_bar[stage], kb * kGemmBK, m_t * kGemmBM,
-                                kEvictLast);
-                    tma_load_2d(smem_w + stage * W_BYTES, &tmap_w, &full_bar[stage], kb * kGemmBK, n_t * BN,
-                                m_tiles > 1 ? kEvictNormal : kEvictFirst);
+                    if (!(args.debug_skip & 1))
+                        tma_load_2d(smem_a + stage * A_BYTES, &tmap_a, &full_bar[stage], kb * kGemmBK, m_t * kGemmBM,
+                                    kEvictLast);
+                    if (args.w_tiled)
+                        tma_load_3d(smem_w + stage * W_BYTES, &tmap_w, &full_bar[stage], 0, kb * 32, n_t * (BN / 32),
+                                    m_tiles > 1 ? kEvictNormal : kEvictFirst);
+                    else
+                        tma_load_2d(smem_w + stage * W_BYTES, &tmap_w, &full_bar[stage], kb * kGemmBK, n_t * BN,
+                                    m_tiles > 1 ? kEvictNormal : kEvictFirst);
                     if (++stage == STAGES) {
                         stage = 0;
                         phase ^= 1;
@@ -442,10 +456,12 @@ gemm_tn_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
                     tc_fence_after();
                     const uint64_t da = make_desc_kmajor_sw128(smem_u32(smem_a + stage * A_BYTES));
                     const uint64_t dw = make_desc_kmajor_sw128(smem_u32(smem_w + stage * W_BYTES));
+                    if (!(args.debug_skip & 2)) {
 #pragma unroll
-                    for (int k = 0; k < kGemmBK / 16; ++k) {
-                        // +32 B per K=16 step inside the 128 B swizzle atom (address field is in 16 B units)
-                        umma_f16_ss(d_tmem, da + 2 * k, dw + 2 * k, IDESC, (kb > kb0 || k > 0) ? 1u : 0u);
+                        for (int k = 0; k < kGemmBK / 16; ++k) {
+                            // +32 B per K=16 step inside the 128 B swizzle atom (address field is in 16 B units)
+                            umma_f16_ss(d_tmem, da + 2 * k, dw + 2 * k, IDESC, (kb > kb0 || k > 0) ? 1u : 0u);
+                        }
                     }
                     umma_commit(&empty_bar[stage]);
                     if (++stage == STAGES) {

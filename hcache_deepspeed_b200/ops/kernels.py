@@ -54,6 +54,58 @@ def _check_2d(t: torch.Tensor, name: str) -> None:
         raise ValueError(f"{name} must be 2-D with a contiguous last dimension, got {tuple(t.shape)} / {t.stride()}")
 
 
+class TiledWeight:
+    """A weight matrix ``[N, K]`` stored pre-tiled for TMA: ``data[ceil(N/32), ceil(K/64), 32, 64]`` so that the
+    32x64 block a GEMM tile needs per k-step is one contiguous 4 KB chunk (zero padded at the edges). Streaming a
+    row-major weight fetches 128-byte segments 2*K bytes apart — poor DRAM page locality for decode-size GEMMs
+    that are pure weight streaming; the tiled layout makes every fetch sequential."""
+
+    def __init__(self, data: torch.Tensor, n: int, k: int):
+        self.data, self.n, self.k = data, n, k
+
+    @staticmethod
+    def from_dense(w: torch.Tensor) -> "TiledWeight":
+        n, k = w.shape
+        np_, kp = -(-n // 32) * 32, -(-k // 64) * 64
+        if (np_, kp) != (n, k):
+            wp = w.new_zeros((np_, kp))
+            wp[:n, :k] = w
+            w = wp
+        data = w.view(np_ // 32, 32, kp // 64, 64).permute(0, 2, 1, 3).contiguous()
+        return TiledWeight(data, n, k)
+
+    def to_dense(self) -> torch.Tensor:
+        s, kb = self.data.shape[0], self.data.shape[1]
+        return self.data.permute(0, 2, 1, 3).reshape(s * 32, kb * 64)[:self.n, :self.k]
+
+    def rows_from(self, start: int) -> "TiledWeight":
+        """Zero-copy view of rows ``[start, n)`` (start must be a multiple of 32)."""
+        assert start % 32 == 0
+        return TiledWeight(self.data[start // 32:], self.n - start, self.k)
+
+    @property
+    def shape(self):
+        return (self.n, self.k)
+
+    @property
+    def dtype(self):
+        return self.data.dtype
+
+    @property
+    def device(self):
+        return self.data.device
+
+    def data_ptr(self) -> int:
+        return self.data.data_ptr()
+
+
+def _w(w):
+    """(pointer, ldw) of a weight operand: ldw = -1 marks the tiled layout for the C ABI."""
+    if isinstance(w, TiledWeight):
+        return w.data.data_ptr(), -1
+    return w.data_ptr(), w.stride(0)
+
+
 def gemm_splitk_workspace_bytes(M: int, N: int) -> int:
     return int(native.cuda_lib().hds_gemm_splitk_workspace_bytes(M, N))
 
@@ -64,16 +116,16 @@ def gemm(a: torch.Tensor, w: torch.Tensor, bias: Optional[torch.Tensor] = None, 
     """``out = epilogue(a @ w.T + bias)`` on the tcgen05 GEMM. ``gated``: interleaved (gate, up) columns.
     ``workspace`` (zero-initialised uint8 scratch) enables split-K for decode-size M."""
     _check_2d(a, "a")
-    _check_2d(w, "w")
     M, K = a.shape
     N = w.shape[0]
     assert w.shape[1] == K and w.dtype == a.dtype
+    wp, ldw = _w(w)
     n_out = N // 2 if gated else N
     if out is None:
         out = torch.empty((M, n_out), dtype=a.dtype, device=a.device)
     _check_2d(out, "out")
     lib = native.cuda_lib()
-    rc = lib.hds_gemm(_p(a), a.stride(0), _p(w), w.stride(0), M, N, K, _dt(a), EPI_GATED if gated else EPI_STORE,
+    rc = lib.hds_gemm(_p(a), a.stride(0), wp, ldw, M, N, K, _dt(a), EPI_GATED if gated else EPI_STORE,
                       act, _p(bias), _p(out), out.stride(0), bn, splits, _p(workspace),
                       0 if workspace is None else workspace.numel() * workspace.element_size(), _stream())
     native.check(rc, "hds_gemm")
@@ -87,9 +139,9 @@ def gemm_accum(a: torch.Tensor, w: torch.Tensor, accum: torch.Tensor, bias: Opti
     """``accum (fp32) += a @ w.T``; with ``peer_ptrs`` / ``multicast_ptr`` the epilogue reduces into every
     tensor-parallel rank's buffer over NVLink (fused GEMM -> all-reduce)."""
     _check_2d(a, "a")
-    _check_2d(w, "w")
     M, K = a.shape
     N = w.shape[0]
+    wp, ldw = _w(w)
     assert accum.dtype == torch.float32 and accum.stride(-1) == 1
     if multicast_ptr is not None:
         ptrs, mode = [multicast_ptr], 2
@@ -99,7 +151,7 @@ def gemm_accum(a: torch.Tensor, w: torch.Tensor, accum: torch.Tensor, bias: Opti
         ptrs, mode = [accum.data_ptr()], 0
     arr = (ctypes.c_void_p * len(ptrs))(*ptrs)
     lib = native.cuda_lib()
-    rc = lib.hds_gemm_accum(_p(a), a.stride(0), _p(w), w.stride(0), M, N, K, _dt(a), _p(bias), arr, len(ptrs), mode,
+    rc = lib.hds_gemm_accum(_p(a), a.stride(0), wp, ldw, M, N, K, _dt(a), _p(bias), arr, len(ptrs), mode,
                             accum.stride(0) if accum.dim() == 2 else N, bn, splits, _stream())
     native.check(rc, "hds_gemm_accum")
     _count()
@@ -112,7 +164,8 @@ def restore_kv_proj(latents: torch.Tensor, w_kv: torch.Tensor, kv_cache_layer: t
     _check_2d(latents, "latents")
     T, H = latents.shape
     lib = native.cuda_lib()
-    rc = lib.hds_restore_kv_proj(_p(latents), latents.stride(0), _p(w_kv), w_kv.stride(0), T, H, _dt(latents),
+    wp, ldw = _w(w_kv)
+    rc = lib.hds_restore_kv_proj(_p(latents), latents.stride(0), wp, ldw, T, H, _dt(latents),
                                  _p(bias_kv), _p(kv_cache_layer), _p(tok_pos), _p(tok_slot), _p(inv_freq), n_kv_heads,
                                  head_dim, block_size, 0 if inv_freq is None else 1, _stream())
     native.check(rc, "hds_restore_kv_proj")
@@ -126,7 +179,8 @@ def qkv_rope_proj(x: torch.Tensor, w_qkv: torch.Tensor, q_out: torch.Tensor, kv_
     _check_2d(x, "x")
     T, H = x.shape
     lib = native.cuda_lib()
-    rc = lib.hds_qkv_rope_proj(_p(x), x.stride(0), _p(w_qkv), w_qkv.stride(0), T, H, _dt(x), _p(bias_qkv), _p(q_out),
+    wp, ldw = _w(w_qkv)
+    rc = lib.hds_qkv_rope_proj(_p(x), x.stride(0), wp, ldw, T, H, _dt(x), _p(bias_qkv), _p(q_out),
                                _p(kv_cache_layer), _p(tok_pos), _p(tok_slot), _p(inv_freq), n_q_heads, n_kv_heads,
                                head_dim, block_size, 0 if inv_freq is None else 1, _stream())
     native.check(rc, "hds_qkv_rope_proj")

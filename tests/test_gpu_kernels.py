@@ -58,6 +58,27 @@ def test_gemm_store_splitk(M, N, K_, bn, splits, gated):
     assert int(ws.view(torch.int32).abs().max()) == 0
 
 
+@pytest.mark.parametrize("M,N,K_", [(8, 4096, 4096), (64, 1000, 520), (300, 2 * 688, 1024), (1, 96, 64)])
+def test_gemm_tiled_weights(M, N, K_):
+    """pre-tiled weight layout: same results as the row-major operand for store / gated / accum epilogues"""
+    torch.manual_seed(13)
+    k = K()
+    a, w, b = rand(M, K_), rand(N, K_, scale=K_ ** -0.5), rand(N)
+    wt = k.TiledWeight.from_dense(w)
+    torch.testing.assert_close(wt.to_dense(), w, rtol=0, atol=0)
+    want = ref.gemm(a, w, bias=b, out_dtype=torch.float32)
+    torch.testing.assert_close(k.gemm(a, wt, bias=b).float(), want, **tol(torch.bfloat16))
+    if N % 2 == 0:
+        wantg = ref.gemm(a, w, act=3, gated=True, out_dtype=torch.float32)
+        torch.testing.assert_close(k.gemm(a, wt, act=3, gated=True).float(), wantg, **tol(torch.bfloat16))
+    acc = torch.zeros(M, N, device="cuda")
+    k.gemm_accum(a, wt, acc, bias=b)
+    torch.testing.assert_close(acc, want, rtol=2e-3, atol=2e-3)
+    if N >= 64:
+        sub = wt.rows_from(32)
+        torch.testing.assert_close(k.gemm(a, sub).float(), ref.gemm(a, w[32:], out_dtype=torch.float32), **tol(torch.bfloat16))
+
+
 @pytest.mark.parametrize("act", [1, 2, 3, 4])
 def test_gemm_bias_act(act):
     torch.manual_seed(1)

@@ -98,6 +98,28 @@ def bench_decode_gemm():
             report(f"cublas_decode M{M} N{N} K{Kd}", med, mn, bytes_=wbytes)
 
 
+def bench_tiled():
+    """row-major vs pre-tiled weights on the decode / short-prefill GEMM shapes of Llama-2-7B"""
+    for M in (8, 64, 4096):
+        for (N, Kd, kind) in [(12288, 4096, "store"), (22016, 4096, "gated"), (4096, 4096, "accum"), (4096, 11008, "accum")]:
+            a, w = rand(M, Kd), rand(N, Kd, scale=Kd ** -0.5)
+            wt = K.TiledWeight.from_dense(w)
+            wbytes = N * Kd * 2
+            for name, ww in (("rowmajor", w), ("tiled", wt)):
+                if kind == "accum":
+                    acc = torch.zeros(M, N, device=dev, dtype=torch.float32)
+                    med, mn = timeit(lambda: K.gemm_accum(a, ww, acc))
+                else:
+                    out = torch.empty(M, N // 2 if kind == "gated" else N, device=dev, dtype=torch.bfloat16)
+                    ws = torch.zeros(K.gemm_splitk_workspace_bytes(min(M, 128), N), dtype=torch.uint8, device=dev)
+                    med, mn = timeit(lambda: K.gemm(a, ww, act=3 if kind == "gated" else 0, gated=kind == "gated", out=out,
+                                                    workspace=ws if M <= 128 else None))
+                if M <= 128:
+                    report(f"{name} {kind} M{M} N{N} K{Kd}", med, mn, bytes_=wbytes)
+                else:
+                    report(f"{name} {kind} M{M} N{N} K{Kd}", med, mn, flops=2.0 * M * N * Kd)
+
+
 def bench_restore():
     for (T, H, n_kv, d) in [(4096, 4096, 32, 128), (4096, 5120, 40, 128), (1024, 4096, 32, 128)]:
         bs = 64
@@ -186,7 +208,7 @@ def bench_norm():
 if __name__ == "__main__":
     which = sys.argv[1:] or ["gemm", "decode_gemm", "restore", "attn_decode", "attn_prefill", "norm"]
     table = {"gemm": bench_gemm, "decode_gemm": bench_decode_gemm, "restore": bench_restore,
-             "attn_decode": bench_attention_decode, "attn_prefill": bench_attention_prefill, "norm": bench_norm}
+             "attn_decode": bench_attention_decode, "tiled": bench_tiled, "attn_prefill": bench_attention_prefill, "norm": bench_norm}
     for w in which:
         table[w]()
     os.makedirs("gpurun_out", exist_ok=True)

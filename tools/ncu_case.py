@@ -33,6 +33,12 @@ elif case == "decode_gemm":
     a, w = rand(M, Kd), rand(N, Kd, scale=Kd ** -0.5)
     out = torch.empty(M, N, device=dev, dtype=torch.bfloat16)
     fn = lambda: K.gemm(a, w, out=out, bn=128)
+elif case == "decode_gated":
+    M, N, Kd = 8, 22016, 4096
+    a, w = rand(M, Kd), rand(N, Kd, scale=Kd ** -0.5)
+    out = torch.empty(M, N // 2, device=dev, dtype=torch.bfloat16)
+    ws = torch.zeros(K.gemm_splitk_workspace_bytes(M, N), dtype=torch.uint8, device=dev)
+    fn = lambda: K.gemm(a, w, act=3, gated=True, out=out, workspace=ws)
 elif case == "gemm":
     M, N, Kd = 4096, 12288, 4096
     a, w = rand(M, Kd), rand(N, Kd, scale=Kd ** -0.5)
