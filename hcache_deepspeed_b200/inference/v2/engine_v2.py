@@ -147,6 +147,44 @@ class InferenceEngineV2:
         for uid, _, _ in todo:
             self._state_manager.get_sequence(uid).post_forward()
 
+    def restore_session(self, uid: int, tokens: torch.Tensor, hidden: Optional[torch.Tensor] = None,
+                        hidden_layers: Sequence[int] = (), kv: Optional[torch.Tensor] = None,
+                        kv_layers: Sequence[int] = (), recompute_layers: Sequence[int] = (),
+                        defer: Optional[bool] = None) -> None:
+        """Bring one session's context back following a mixed plan (``hcache/planner.py``):
+
+        * ``recompute_layers`` — must be the prefix ``0..r-1``: recomputed from ``tokens`` (uses the GPU while the
+          host link is the bottleneck);
+        * ``kv_layers`` — ``kv [n_blocks, len(kv_layers), 2, kv_heads, block, head_dim]`` copied into the pages;
+        * ``hidden_layers`` — ``hidden [len(hidden_layers), n_tokens, hidden]`` through the K/V projection kernel.
+        """
+        tokens = tokens.reshape(-1)
+        n = int(tokens.numel())
+        rl = list(recompute_layers)
+        if rl != list(range(len(rl))):
+            raise ValueError("recomputed layers must form a prefix 0..r-1 (layer l needs layer l-1's output)")
+        model = self._model
+        model.finish_pending_restore()
+        if len(rl) + len(list(hidden_layers)) + len(list(kv_layers)) != model.spec.n_layers:
+            raise ValueError("the plan does not cover every layer exactly once")
+        self._batch.clear()
+        seq = self._state_manager.get_or_create_sequence(uid)
+        if seq.seen_tokens != 0:
+            raise RuntimeError(f"sequence {uid} already holds {seq.seen_tokens} tokens; flush it before restoring")
+        model.maybe_allocate_kv(seq, n)
+        seq.pre_forward(n)
+        self._batch.insert_sequence(seq, tokens)
+        self._batch.finalize()
+        if rl:
+            model.forward(self._batch, capture=False, n_layers_limit=len(rl))
+        if len(list(kv_layers)):
+            model.restore_kv_pages(seq.all_block_ids, kv, list(kv_layers))
+        if len(list(hidden_layers)):
+            if defer is None:
+                defer = self._config.hcache.overlap_restore
+            model.restore_kv(self._batch, [hidden], layers=list(hidden_layers), defer=bool(defer))
+        seq.post_forward()
+
     # ------------------------------------------------------------------------------------------------
     # forward
     # ------------------------------------------------------------------------------------------------

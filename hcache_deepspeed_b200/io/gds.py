@@ -1,0 +1,130 @@
+"""GPUDirect Storage path (cuFile) for the NVMe tier: file -> device memory without a host bounce buffer.
+
+Counterpart of the reference's ``gds_handle`` (``csrc/gds/py_lib/deepspeed_gds_op.cpp:22-144``,
+``deepspeed_py_gds_handle.cpp:59-62``): ``cuFileDriverOpen``, ``cuFileHandleRegister``, ``cuFileBufRegister``,
+``cuFileRead`` / ``cuFileWrite`` at explicit file and device offsets. libcufile is bound with ctypes at run time;
+when the library, the nvidia-fs driver or a GDS-capable file system is missing, :func:`gds_available` is False and
+the store falls back to the async-I/O + pinned-staging path.
+"""
+from __future__ import annotations
+
+import ctypes
+import os
+from typing import Optional
+
+import torch
+
+_lib: Optional[ctypes.CDLL] = None
+_driver_open = False
+
+
+class _CUfileDescr(ctypes.Structure):
+    _fields_ = [("type", ctypes.c_int), ("fd", ctypes.c_int), ("_pad", ctypes.c_char * 8), ("fs_ops", ctypes.c_void_p)]
+
+
+class _CUfileError(ctypes.Structure):
+    _fields_ = [("err", ctypes.c_int), ("cu_err", ctypes.c_int)]
+
+
+def _load() -> Optional[ctypes.CDLL]:
+    global _lib
+    if _lib is not None:
+        return _lib
+    for name in ("libcufile.so.0", "libcufile.so", "/usr/local/cuda/lib64/libcufile.so"):
+        try:
+            lib = ctypes.CDLL(name)
+        except OSError:
+            continue
+        lib.cuFileDriverOpen.restype = _CUfileError
+        lib.cuFileDriverClose.restype = _CUfileError
+        lib.cuFileHandleRegister.restype = _CUfileError
+        lib.cuFileHandleRegister.argtypes = [ctypes.POINTER(ctypes.c_void_p), ctypes.POINTER(_CUfileDescr)]
+        lib.cuFileHandleDeregister.argtypes = [ctypes.c_void_p]
+        lib.cuFileBufRegister.restype = _CUfileError
+        lib.cuFileBufRegister.argtypes = [ctypes.c_void_p, ctypes.c_size_t, ctypes.c_int]
+        lib.cuFileBufDeregister.restype = _CUfileError
+        lib.cuFileBufDeregister.argtypes = [ctypes.c_void_p]
+        for fn in (lib.cuFileRead, lib.cuFileWrite):
+            fn.restype = ctypes.c_ssize_t
+            fn.argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_size_t, ctypes.c_longlong, ctypes.c_longlong]
+        _lib = lib
+        return lib
+    return None
+
+
+def gds_available() -> bool:
+    """True when libcufile loads and its driver opens (needs a GPU and, for real DMA, nvidia-fs)."""
+    global _driver_open
+    if not torch.cuda.is_available():
+        return False
+    lib = _load()
+    if lib is None:
+        return False
+    if not _driver_open:
+        st = lib.cuFileDriverOpen()
+        _driver_open = st.err == 0
+    return _driver_open
+
+
+class GDSHandle:
+    """Synchronous cuFile reads / writes between a file and a device tensor (call from an I/O thread / side stream
+    owner; cuFile itself is synchronous with respect to the calling thread)."""
+
+    def __init__(self) -> None:
+        if not gds_available():
+            raise RuntimeError("GPUDirect Storage is not available on this system (libcufile / nvidia-fs)")
+        self._lib = _load()
+        self._registered = {}
+
+    def pin_device_tensor(self, t: torch.Tensor) -> None:
+        """Register a device buffer once so repeated transfers skip per-call registration."""
+        st = self._lib.cuFileBufRegister(ctypes.c_void_p(t.data_ptr()), t.numel() * t.element_size(), 0)
+        if st.err != 0:
+            raise RuntimeError(f"cuFileBufRegister failed: {st.err}")
+        self._registered[t.data_ptr()] = t
+
+    def unpin_device_tensor(self, t: torch.Tensor) -> None:
+        if self._registered.pop(t.data_ptr(), None) is not None:
+            self._lib.cuFileBufDeregister(ctypes.c_void_p(t.data_ptr()))
+
+    def new_pinned_device_tensor(self, num_elem: int, example: torch.Tensor) -> torch.Tensor:
+        t = torch.empty(num_elem, dtype=example.dtype, device=example.device)
+        self.pin_device_tensor(t)
+        return t
+
+    def _open(self, path: str, write: bool):
+        flags = (os.O_WRONLY | os.O_CREAT if write else os.O_RDONLY) | getattr(os, "O_DIRECT", 0)
+        fd = os.open(path, flags, 0o644)
+        descr = _CUfileDescr(type=1, fd=fd)  # CU_FILE_HANDLE_TYPE_OPAQUE_FD
+        handle = ctypes.c_void_p()
+        st = self._lib.cuFileHandleRegister(ctypes.byref(handle), ctypes.byref(descr))
+        if st.err != 0:
+            os.close(fd)
+            raise RuntimeError(f"cuFileHandleRegister({path}) failed: {st.err}")
+        return fd, handle
+
+    def sync_pread(self, device_tensor: torch.Tensor, path: str, file_offset: int = 0, nbytes: Optional[int] = None,
+                   device_offset: int = 0) -> int:
+        n = nbytes if nbytes is not None else device_tensor.numel() * device_tensor.element_size()
+        fd, handle = self._open(path, write=False)
+        try:
+            got = self._lib.cuFileRead(handle, ctypes.c_void_p(device_tensor.data_ptr()), n, file_offset, device_offset)
+        finally:
+            self._lib.cuFileHandleDeregister(handle)
+            os.close(fd)
+        if got < 0:
+            raise OSError(f"cuFileRead failed with {got}")
+        return int(got)
+
+    def sync_pwrite(self, device_tensor: torch.Tensor, path: str, file_offset: int = 0, nbytes: Optional[int] = None,
+                    device_offset: int = 0) -> int:
+        n = nbytes if nbytes is not None else device_tensor.numel() * device_tensor.element_size()
+        fd, handle = self._open(path, write=True)
+        try:
+            got = self._lib.cuFileWrite(handle, ctypes.c_void_p(device_tensor.data_ptr()), n, file_offset, device_offset)
+        finally:
+            self._lib.cuFileHandleDeregister(handle)
+            os.close(fd)
+        if got < 0:
+            raise OSError(f"cuFileWrite failed with {got}")
+        return int(got)

@@ -302,11 +302,13 @@ class RaggedTransformer:
         self._delta_idx = (self._delta_idx + 1) % len(self._delta_bufs)
         return d32
 
-    def forward(self, batch: RaggedBatchWrapper, capture: bool = False,
-                all_logits: bool = False) -> Tuple[torch.Tensor, Optional[torch.Tensor]]:
+    def forward(self, batch: RaggedBatchWrapper, capture: bool = False, all_logits: bool = False,
+                n_layers_limit: Optional[int] = None) -> Tuple[torch.Tensor, Optional[torch.Tensor]]:
         """One ragged forward. Returns ``(logits [n_seqs, vocab], latents)`` where latents is the device view
         ``[n_layers, n_tokens, hidden]`` of the captured QKV inputs (None when capture is off).
-        ``all_logits``: unembed every token instead of each sequence's last one (``[n_tokens, vocab]``; v1 API)."""
+        ``all_logits``: unembed every token instead of each sequence's last one (``[n_tokens, vocab]``; v1 API).
+        ``n_layers_limit``: run only the first layers (writing their K/V) and return ``(None, latents)`` — the
+        recomputed prefix of a mixed HCache restore plan."""
         s, w, ops = self.spec, self.w, self.ops
         T, S = batch.current_tokens, batch.current_sequences
         if capture and self.latent_buf is None:
@@ -319,7 +321,8 @@ class RaggedTransformer:
         kv = self._state_manager
         bs = kv.kv_block_size
         two_norms = (not s.parallel_residual) or s.parallel_two_norms
-        for li in range(s.n_layers):
+        n_run = s.n_layers if n_layers_limit is None else min(n_layers_limit, s.n_layers)
+        for li in range(n_run):
             lw = w.layers[li]
             xn = (self.latent_buf[li] if capture else self.xn)[:T]
             ops.norm(resid, lw.norm1_g, xn, beta=lw.norm1_b, delta=pending, zero_delta=True,
@@ -343,6 +346,10 @@ class RaggedTransformer:
                 x2 = ops.norm(resid, lw.norm2_g, self.xn2[:T], beta=lw.norm2_b, delta=d1, zero_delta=True, res_out=resid,
                               eps=s.norm_eps, layer_norm=ln)
                 pending = self._mlp(x2, lw, T, force_accum=False)
+        if n_layers_limit is not None:
+            if pending is not None and pending.dtype == torch.float32:
+                pending.zero_()  # the partial sums of the last executed layer are not consumed by a norm
+            return None, (self.latent_buf[:n_run, :T] if capture else None)
         if self._pending_restore is not None:
             self.finish_pending_restore()
         # ---- last-token logits ----
