@@ -36,6 +36,13 @@ class RestorePlan:
     kinds: List[str]                      # per layer: "hidden" | "kv" | "none" (recompute)
     io_s: float
     compute_s: float
+    layer_fwd_s: float = 0.0              # modelled time to recompute one layer
+    layer_hidden_io_s: float = 0.0        # modelled time to transfer one layer's hidden states
+
+    @property
+    def interleave(self) -> float:
+        """Saved layers whose transfer completes while one prefix layer is recomputed."""
+        return self.layer_fwd_s / self.layer_hidden_io_s if self.layer_hidden_io_s > 0 else 0.0
 
     @property
     def est_seconds(self) -> float:
@@ -60,12 +67,16 @@ def _costs(spec: ArchSpec, n_tokens: int, link: LinkModel, from_nvme: bool, elem
 
 
 def plan_restore(spec: ArchSpec, n_tokens: int, link: Optional[LinkModel] = None, from_nvme: bool = False,
-                 elem: int = 2, allow_recompute: bool = True, allow_kv: bool = True) -> RestorePlan:
+                 elem: int = 2, allow_recompute: bool = True, allow_kv: bool = True,
+                 extra_compute_s: float = 0.0) -> RestorePlan:
     """Choose per-layer restore methods minimising ``max(io, compute)``.
 
     Layout of the plan: the first ``r`` layers are recomputed (optional), then ``n_h`` layers come from hidden
     states, the remaining ``n_k`` from KV pages. All ``(r, n_h)`` splits are enumerated (L is at most a few
     hundred), so the result is optimal for the cost model above.
+
+    ``extra_compute_s``: GPU time that shares the restore window — with deferred restore the new turn's prefill is
+    interleaved with the projections, so its duration belongs on the compute side of the balance.
     """
     link = link or LinkModel()
     L = spec.n_layers
@@ -77,7 +88,7 @@ def plan_restore(spec: ArchSpec, n_tokens: int, link: Optional[LinkModel] = None
             if n_k and not allow_kv:
                 continue
             io = n_h * a + n_k * b
-            comp = r * f + n_h * c
+            comp = r * f + n_h * c + extra_compute_s
             t = max(io, comp)
             # tie-break: fewer stored bytes (prefer whichever of hidden/kv is smaller), then less compute
             stored = n_h * n_tokens * spec.hidden + n_k * n_tokens * 2 * spec.kv_dim
@@ -86,7 +97,7 @@ def plan_restore(spec: ArchSpec, n_tokens: int, link: Optional[LinkModel] = None
                 best = (key, r, n_h, n_k, io, comp)
     _, r, n_h, n_k, io, comp = best
     kinds = ["none"] * r + ["hidden"] * n_h + ["kv"] * n_k
-    return RestorePlan(kinds, io, comp)
+    return RestorePlan(kinds, io, comp, layer_fwd_s=f, layer_hidden_io_s=a)
 
 
 def storage_bytes(spec: ArchSpec, n_tokens: int, plan: RestorePlan, elem: int = 2) -> int:

@@ -43,8 +43,10 @@ class HCacheSessionManager:
         if uid in self._resident:
             return 0
         st = self.store.load(uid)
+        plan = self.plan_for(st.n_tokens)
         self.engine.restore_session(uid, st.tokens, hidden=st.hidden, hidden_layers=st.layers_of("hidden"), kv=st.kv,
-                                    kv_layers=st.layers_of("kv"), recompute_layers=st.layers_of("none"))
+                                    kv_layers=st.layers_of("kv"), recompute_layers=st.layers_of("none"),
+                                    interleave=plan.interleave or 2.5)
         self._resident.add(uid)
         # the hidden states of restored layers are already known: carry them into the next save
         self._live_tokens[uid] = [st.tokens]

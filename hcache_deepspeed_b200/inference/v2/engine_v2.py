@@ -150,13 +150,15 @@ class InferenceEngineV2:
     def restore_session(self, uid: int, tokens: torch.Tensor, hidden: Optional[torch.Tensor] = None,
                         hidden_layers: Sequence[int] = (), kv: Optional[torch.Tensor] = None,
                         kv_layers: Sequence[int] = (), recompute_layers: Sequence[int] = (),
-                        defer: Optional[bool] = None) -> None:
+                        defer: Optional[bool] = None, interleave: float = 2.5) -> None:
         """Bring one session's context back following a mixed plan (``hcache/planner.py``):
 
         * ``recompute_layers`` — must be the prefix ``0..r-1``: recomputed from ``tokens`` (uses the GPU while the
           host link is the bottleneck);
         * ``kv_layers`` — ``kv [n_blocks, len(kv_layers), 2, kv_heads, block, head_dim]`` copied into the pages;
         * ``hidden_layers`` — ``hidden [len(hidden_layers), n_tokens, hidden]`` through the K/V projection kernel.
+
+        ``interleave``: saved layers projected per recomputed layer (layer-forward time / per-layer transfer time).
         """
         tokens = tokens.reshape(-1)
         n = int(tokens.numel())
@@ -175,14 +177,18 @@ class InferenceEngineV2:
         seq.pre_forward(n)
         self._batch.insert_sequence(seq, tokens)
         self._batch.finalize()
-        if rl:
-            model.forward(self._batch, capture=False, n_layers_limit=len(rl))
+        if defer is None:
+            defer = self._config.hcache.overlap_restore
+        n_hidden = len(list(hidden_layers))
+        # start the host-to-device stream of the hidden states FIRST: it then runs under the recomputed prefix
+        if n_hidden:
+            model.restore_kv(self._batch, [hidden], layers=list(hidden_layers), defer=True)
         if len(list(kv_layers)):
             model.restore_kv_pages(seq.all_block_ids, kv, list(kv_layers))
-        if len(list(hidden_layers)):
-            if defer is None:
-                defer = self._config.hcache.overlap_restore
-            model.restore_kv(self._batch, [hidden], layers=list(hidden_layers), defer=bool(defer))
+        if rl:
+            model.forward(self._batch, capture=False, n_layers_limit=len(rl), restore_interleave=interleave)
+        if n_hidden and not defer:
+            model.finish_pending_restore()
         seq.post_forward()
 
     # ------------------------------------------------------------------------------------------------

@@ -303,12 +303,15 @@ class RaggedTransformer:
         return d32
 
     def forward(self, batch: RaggedBatchWrapper, capture: bool = False, all_logits: bool = False,
-                n_layers_limit: Optional[int] = None) -> Tuple[torch.Tensor, Optional[torch.Tensor]]:
+                n_layers_limit: Optional[int] = None,
+                restore_interleave: float = 0.0) -> Tuple[torch.Tensor, Optional[torch.Tensor]]:
         """One ragged forward. Returns ``(logits [n_seqs, vocab], latents)`` where latents is the device view
         ``[n_layers, n_tokens, hidden]`` of the captured QKV inputs (None when capture is off).
         ``all_logits``: unembed every token instead of each sequence's last one (``[n_tokens, vocab]``; v1 API).
         ``n_layers_limit``: run only the first layers (writing their K/V) and return ``(None, latents)`` — the
-        recomputed prefix of a mixed HCache restore plan."""
+        recomputed prefix of a mixed HCache restore plan. With a deferred restore pending, ``restore_interleave``
+        saved layers are projected after each recomputed layer (their transfers complete at that rate), so the
+        copy engine never waits for a free staging slot while the GPU recomputes."""
         s, w, ops = self.spec, self.w, self.ops
         T, S = batch.current_tokens, batch.current_sequences
         if capture and self.latent_buf is None:
@@ -346,6 +349,13 @@ class RaggedTransformer:
                 x2 = ops.norm(resid, lw.norm2_g, self.xn2[:T], beta=lw.norm2_b, delta=d1, zero_delta=True, res_out=resid,
                               eps=s.norm_eps, layer_norm=ln)
                 pending = self._mlp(x2, lw, T, force_accum=False)
+            if n_layers_limit is not None and restore_interleave > 0 and self._pending_restore is not None:
+                st = self._pending_restore
+                target = min(len(st["layers"]), int((li + 1) * restore_interleave))
+                while st["done"] < target:
+                    self._restore_project(st, st["done"])
+                if st["done"] >= len(st["layers"]):
+                    self._pending_restore = None
         if n_layers_limit is not None:
             if pending is not None and pending.dtype == torch.float32:
                 pending.zero_()  # the partial sums of the last executed layer are not consumed by a norm
@@ -465,6 +475,8 @@ class RaggedTransformer:
     def _restore_step(self, li: int) -> None:
         """Called by ``forward`` right before layer ``li`` touches its KV cache."""
         st = self._pending_restore
+        if li not in st["by_layer"]:
+            return
         for i in st["by_layer"].get(li, ()):
             while st["done"] <= i:  # saved layers are consumed in order
                 self._restore_project(st, st["done"])
