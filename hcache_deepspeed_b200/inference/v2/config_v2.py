@@ -42,6 +42,9 @@ class HCacheConfig(DeepSpeedConfigModel):
     overlap_restore: bool = True
     """``restore_kv`` defers its per-layer projections into the next ``put`` so the new turn's prefill overlaps the
     host-to-device transfer of the saved hidden states."""
+    shard_capture: bool = False
+    """Tensor parallel: every rank exports only its 1/tp row slice of each sequence's hidden states (they are
+    replicated on the device), to be passed back to ``restore_kv(..., sharded=True)``."""
     host_ring_bytes: int = 2 << 30
     """Pinned host staging used for asynchronous capture."""
 

@@ -111,7 +111,7 @@ class InferenceEngineV2:
     def restore_kv(self, batch_uids: Iterable[int], batch_tokens: Iterable[torch.Tensor],
                    batch_latents: Iterable[Optional[Union[torch.Tensor, LatentHandle]]],
                    layers: Optional[Sequence[int]] = None, do_checks: bool = True,
-                   defer: Optional[bool] = None) -> None:
+                   defer: Optional[bool] = None, sharded: bool = False) -> None:
         """Rebuild the KV cache of ``batch_uids`` from saved hidden states instead of recomputing the prompt.
 
         ``batch_tokens`` only supply the token counts (ref: engine_v2.py:108-128); ``batch_latents[i]`` is the host
@@ -121,6 +121,10 @@ class InferenceEngineV2:
 
         ``defer`` (default: ``hcache.overlap_restore``): only start the transfers now and let the next ``put``
         interleave each layer's K/V projection with its own layers (hides the new turn's prefill under PCIe time).
+
+        ``sharded`` (tensor parallel, one sequence per call): every rank passes only ITS row slice of the hidden
+        states (``latent_row_range``), moves 1/tp of the bytes over its own PCIe link, and the projection kernels
+        gather the slices from peer memory over NVLink — restore bandwidth scales with the number of GPUs.
         """
         uids, toks, lats = list(batch_uids), list(batch_tokens), list(batch_latents)
         todo = [(u, t, (l.wait() if isinstance(l, LatentHandle) else l)) for u, t, l in zip(uids, toks, lats)
@@ -132,6 +136,8 @@ class InferenceEngineV2:
             if check != SchedulingResult.Success:
                 raise SchedulingError(check)
         for u, t, l in todo:
+            if sharded:
+                continue
             if l.dim() != 3 or int(l.shape[1]) != int(t.numel()):
                 raise ValueError(f"latents of uid {u} have shape {tuple(l.shape)}, expected [layers, {int(t.numel())}, hidden]")
         self._batch.clear()
@@ -143,7 +149,7 @@ class InferenceEngineV2:
         self._batch.finalize()
         if defer is None:
             defer = self._config.hcache.overlap_restore
-        self._model.restore_kv(self._batch, [l for _, _, l in todo], layers=layers, defer=bool(defer))
+        self._model.restore_kv(self._batch, [l for _, _, l in todo], layers=layers, defer=bool(defer), sharded=sharded)
         for uid, _, _ in todo:
             self._state_manager.get_sequence(uid).post_forward()
 
@@ -229,29 +235,53 @@ class InferenceEngineV2:
         return logits, latents
 
     def _export_latents(self, latent_dev: torch.Tensor) -> List:
-        """Device ``[L, T, H]`` -> one pinned host tensor, split into per-sequence views (engine_v2.py:172-179)."""
+        """Device ``[L, T, H]`` -> pinned host memory, split into per-sequence views (engine_v2.py:172-179).
+        Under tensor parallelism the hidden states are replicated: rank 0 exports them (other ranks return None),
+        or with ``hcache.shard_capture`` every rank exports its 1/tp row slice of each sequence."""
         shadow = self._batch.inflight_seq_descriptors_shadow
         mode = self._config.hcache.capture
-        if self._model.tp_size > 1 and self._model.tp_rank != 0:
-            return [None] * len(shadow)  # replicated across ranks: one host copy is enough
+        tp, rank = self._model.tp_size, self._model.tp_rank
+        shard = tp > 1 and self._config.hcache.shard_capture
+        if tp > 1 and rank != 0 and not shard:
+            return [None] * len(shadow)
+        spans = [(b, n) for b, n, _ in shadow]
+        if shard:
+            from ...models.transformer import shard_rows
+            spans = []
+            for b, n, _ in shadow:
+                lo, hi, _ = shard_rows(n, tp, rank)
+                spans.append((b + lo, hi - lo))
         if latent_dev.device.type != "cuda":
-            host = latent_dev.clone()
-            return [host[:, b:b + n] for b, n, _ in shadow]
-        host = torch.empty(latent_dev.shape, dtype=latent_dev.dtype, pin_memory=True)
+            return [latent_dev[:, b:b + n].clone() for b, n in spans]
+        total = sum(n for _, n in spans)
+        host = torch.empty((latent_dev.shape[0], total, latent_dev.shape[2]), dtype=latent_dev.dtype, pin_memory=True)
         comp = torch.cuda.current_stream()
         cs = self._capture_stream
         cs.wait_stream(comp)
+        views, off = [], 0
         with torch.cuda.stream(cs):
-            host.copy_(latent_dev, non_blocking=True)
+            contiguous = all(spans[i][0] + spans[i][1] == spans[i + 1][0] for i in range(len(spans) - 1))
+            if contiguous and spans:
+                host.copy_(latent_dev[:, spans[0][0]:spans[0][0] + total], non_blocking=True)
+            for b, n in spans:
+                if not contiguous and n:
+                    host[:, off:off + n].copy_(latent_dev[:, b:b + n], non_blocking=True)
+                views.append(host[:, off:off + n])
+                off += n
             ev = torch.cuda.Event()
             ev.record(cs)
         # the model's latent buffer is reused by the next forward: make that forward wait for this copy
         comp.wait_event(ev)
-        views = [host[:, b:b + n] for b, n, _ in shadow]
         if mode == "async":
             return [LatentHandle(v, ev) for v in views]
         ev.synchronize()
         return views
+
+    def latent_row_range(self, n_tokens: int) -> Tuple[int, int]:
+        """Rows of a sequence's hidden states this TP rank stores / passes to a sharded restore."""
+        from ...models.transformer import shard_rows
+        lo, hi, _ = shard_rows(n_tokens, self._model.tp_size, self._model.tp_rank)
+        return lo, hi
 
     # ------------------------------------------------------------------------------------------------
     # scheduling helpers

@@ -41,6 +41,14 @@ def ceil_div(a: int, b: int) -> int:
     return -(-a // b)
 
 
+def shard_rows(n_tokens: int, tp_size: int, tp_rank: int) -> Tuple[int, int, int]:
+    """Row range ``[start, end)`` of a sequence's hidden states owned by a TP rank, and the per-rank stride.
+    Strides are multiples of 128 (one GEMM m-tile) so a tile never straddles two ranks."""
+    per = ceil_div(ceil_div(n_tokens, tp_size), 128) * 128
+    start = min(n_tokens, tp_rank * per)
+    return start, min(n_tokens, start + per), per
+
+
 class TPComm:
     """How row-parallel partial sums meet across tensor-parallel ranks (see parallel/tp_comm.py)."""
     fused = False
@@ -184,6 +192,11 @@ class RaggedTransformer:
             self.ws_large = torch.zeros(worst_l, dtype=torch.uint8, device=dev)
             self.io_stream = torch.cuda.Stream(device=dev)
             self.restore_stage = buf(RESTORE_SLOTS, T, H)
+            self.restore_stage_sym = None
+            if self.tp_size > 1 and getattr(self.comm, "fused", False):
+                # per-rank slice of the staging ring in symmetric memory: peers' restore kernels read it over NVLink
+                self._sym_rows = ceil_div(ceil_div(T, self.tp_size), 128) * 128
+                self.restore_stage_sym = self.comm.alloc_symmetric((RESTORE_SLOTS, self._sym_rows, H), dt)
             self.restore_pos = torch.zeros(T, dtype=torch.int32, device=dev)
             self.restore_slot = torch.zeros(T, dtype=torch.int32, device=dev)
             self.ev_loaded = [torch.cuda.Event() for _ in range(RESTORE_SLOTS)]
@@ -395,7 +408,7 @@ class RaggedTransformer:
         return lw.w_qkv[r0:], (lw.b_qkv[r0:] if lw.b_qkv is not None else None)
 
     def restore_kv(self, batch: RaggedBatchWrapper, latents: Sequence[torch.Tensor],
-                   layers: Optional[Sequence[int]] = None, defer: bool = False) -> None:
+                   layers: Optional[Sequence[int]] = None, defer: bool = False, sharded: bool = False) -> None:
         """Rebuild the paged K/V of the batch's tokens from saved hidden states.
 
         ``latents``: one host tensor per sequence of the batch, ``[n_saved_layers, n_tokens_i, hidden]``, whose
@@ -411,7 +424,13 @@ class RaggedTransformer:
         s, ops = self.spec, self.ops
         layers = list(range(s.n_layers)) if layers is None else list(layers)
         T = batch.current_tokens
-        if sum(int(l.shape[1]) for l in latents) != T:
+        if sharded:
+            if self.restore_stage_sym is None or len(latents) != 1 or batch.current_sequences != 1:
+                raise ValueError("sharded restore needs fused tensor parallelism and exactly one sequence per call")
+            lo, hi, _ = shard_rows(T, self.tp_size, self.tp_rank)
+            if int(latents[0].shape[1]) != hi - lo:
+                raise ValueError(f"rank {self.tp_rank} must pass rows [{lo}, {hi}) of the hidden states")
+        elif sum(int(l.shape[1]) for l in latents) != T:
             raise ValueError("latents do not cover the tokens of the restore batch")
         pos, slot = batch.tok_pos(), batch.tok_slot()
         kv = self._state_manager
@@ -429,7 +448,8 @@ class RaggedTransformer:
         # private copy of the per-token metadata: the batch wrapper's buffers are rewritten by the next forward
         self.restore_pos[:T].copy_(pos, non_blocking=True)
         self.restore_slot[:T].copy_(slot, non_blocking=True)
-        st = {"T": T, "layers": layers, "latents": list(latents), "issued": 0, "done": 0, "by_layer": {}}
+        st = {"T": T, "layers": layers, "latents": list(latents), "issued": 0, "done": 0, "by_layer": {},
+              "sharded": bool(sharded)}
         for i, li in enumerate(layers):
             st["by_layer"].setdefault(li, []).append(i)
         self._pending_restore = st
@@ -443,7 +463,7 @@ class RaggedTransformer:
         i = st["issued"]
         k = i % RESTORE_SLOTS
         io = self.io_stream
-        stage = self.restore_stage[k]
+        stage = self.restore_stage_sym[k] if st["sharded"] else self.restore_stage[k]
         with torch.cuda.stream(io):
             if i >= RESTORE_SLOTS:
                 io.wait_event(self.ev_consumed[k])
@@ -464,9 +484,19 @@ class RaggedTransformer:
         comp = torch.cuda.current_stream()
         comp.wait_event(self.ev_loaded[k])
         wk, bk = self.kv_weight(li)
-        self.ops.restore_kv_proj(self.restore_stage[k][:T], wk, bk, kv.get_cache(li), self.restore_pos[:T],
-                                 self.restore_slot[:T], self.inv_freq, self.n_kv, self.d, s.rot_dim, kv.kv_block_size,
-                                 scratch=self.kv_scratch[:T] if self.kv_scratch is not None else None)
+        if st["sharded"]:
+            # every rank's slice of this layer has landed in its own HBM -> gather inside the projection kernel
+            _, _, per = shard_rows(T, self.tp_size, self.tp_rank)
+            self.comm.barrier()
+            ptrs = self.comm.peer_ptrs_raw(self.restore_stage_sym, byte_offset=k * self._sym_rows * s.hidden * 2)
+            self.ops.k.restore_kv_proj_peers(ptrs, per, T, s.hidden, self.dtype, wk, kv.get_cache(li), self.restore_pos[:T],
+                                             self.restore_slot[:T], self.inv_freq, self.n_kv, self.d, kv.kv_block_size,
+                                             bias_kv=bk)
+            self.comm.barrier()  # peers are done reading my slot before it is refilled
+        else:
+            self.ops.restore_kv_proj(self.restore_stage[k][:T], wk, bk, kv.get_cache(li), self.restore_pos[:T],
+                                     self.restore_slot[:T], self.inv_freq, self.n_kv, self.d, s.rot_dim, kv.kv_block_size,
+                                     scratch=self.kv_scratch[:T] if self.kv_scratch is not None else None)
         self.ev_consumed[k].record(comp)
         st["done"] = i + 1
         if st["issued"] < len(st["layers"]):

@@ -6,9 +6,13 @@
 
 namespace hds {
 
+static thread_local const TmapSet* g_peer_maps = nullptr;  // set by the peer-sharded entry point around its launch
+static thread_local int g_peer_rows = 0, g_peer_count = 0;
+
 template <int BN, int EPI, bool kBf16, int HD = 128, int AM = 128>
 static int launch_gemm_inst(const CUtensorMap& ta, const CUtensorMap& tw, const GemmArgs& args, int grid,
                             cudaStream_t stream) {
+    static const TmapSet kNoPeers = {};
     auto kern = gemm_tn_kernel<BN, EPI, kBf16, HD, AM>;
     static bool configured[64] = {false};
     int dev = 0;
@@ -18,7 +22,7 @@ static int launch_gemm_inst(const CUtensorMap& ta, const CUtensorMap& tw, const 
                                             static_cast<int>(gemm_smem_bytes(BN, AM))));
         configured[dev & 63] = true;
     }
-    kern<<<grid, kGemmThreads, gemm_smem_bytes(BN, AM), stream>>>(ta, tw, args);
+    kern<<<grid, kGemmThreads, gemm_smem_bytes(BN, AM), stream>>>(ta, tw, args, g_peer_maps ? *g_peer_maps : kNoPeers);
     HDS_CHECK_CUDA(cudaGetLastError());
     return HDS_OK;
 }
@@ -123,6 +127,8 @@ static int prepare(GemmArgs& g, Operands& ops, const void* A, int64_t lda, const
     g.K = K;
     static const int debug_skip = getenv("HDS_GEMM_DEBUG") ? atoi(getenv("HDS_GEMM_DEBUG")) : 0;
     g.debug_skip = debug_skip;
+    g.a_peers = g_peer_count;
+    g.a_rows_per_peer = g_peer_rows;
     const int kb_total = (K + kGemmBK - 1) / kGemmBK;
     if (splits < 1) splits = 1;
     if (splits > kb_total) splits = kb_total;
@@ -280,6 +286,38 @@ extern "C" int hds_restore_kv_proj(const void* latents, int64_t ld_latents, cons
                                    int n_kv_heads, int head_dim, int block_size, int do_rope, void* stream) {
     return gemm_rope_common(false, latents, ld_latents, w_kv, ldw, T, H, dtype, bias_kv, nullptr, kv_cache_layer,
                             tok_pos, tok_slot, inv_freq, 0, n_kv_heads, head_dim, block_size, do_rope, stream);
+}
+
+extern "C" int hds_restore_kv_proj_peers(const void* const* latent_ptrs, int n_peers, int rows_per_peer,
+                                         int64_t ld_latents, const void* w_kv, int64_t ldw, int T, int H, int dtype,
+                                         const void* bias_kv, void* kv_cache_layer, const int32_t* tok_pos,
+                                         const int32_t* tok_slot, const float* inv_freq, int n_kv_heads, int head_dim,
+                                         int block_size, int do_rope, void* stream) {
+    HDS_REQUIRE(n_peers >= 1 && n_peers <= kMaxPeers, "restore_kv_proj_peers: 1..8 peers");
+    HDS_REQUIRE(rows_per_peer > 0 && rows_per_peer % kGemmBM == 0, "restore_kv_proj_peers: rows_per_peer must be a multiple of 128");
+    HDS_REQUIRE(static_cast<int64_t>(n_peers) * rows_per_peer >= T, "restore_kv_proj_peers: peers do not cover T rows");
+    HDS_REQUIRE(dtype == 0 || dtype == 1, "restore_kv_proj_peers: dtype must be 0 (bf16) or 1 (fp16)");
+    TmapSet set;
+    memset(&set, 0, sizeof(set));
+    for (int p = 0; p < n_peers; ++p) {
+        const int64_t first = static_cast<int64_t>(p) * rows_per_peer;
+        int64_t rows = T - first;
+        if (rows > rows_per_peer) rows = rows_per_peer;
+        if (rows <= 0) rows = 1;  // a peer without rows is never addressed; keep the descriptor valid
+        const uint32_t box_rows = T < kGemmBM ? static_cast<uint32_t>(((T + 7) / 8) * 8) : kGemmBM;  // as prepare()
+        int rc = make_tmap_2d_16b(&set.m[p], latent_ptrs[p], static_cast<uint64_t>(H), static_cast<uint64_t>(rows),
+                                  static_cast<uint64_t>(ld_latents) * 2, kGemmBK, box_rows, dtype == 0);
+        if (rc) return rc;
+    }
+    g_peer_maps = &set;
+    g_peer_rows = rows_per_peer;
+    g_peer_count = n_peers;
+    const int rc = gemm_rope_common(false, latent_ptrs[0], ld_latents, w_kv, ldw, T, H, dtype, bias_kv, nullptr,
+                                    kv_cache_layer, tok_pos, tok_slot, inv_freq, 0, n_kv_heads, head_dim, block_size,
+                                    do_rope, stream);
+    g_peer_maps = nullptr;
+    g_peer_count = 0;
+    return rc;
 }
 
 extern "C" int hds_qkv_rope_proj(const void* x, int64_t ldx, const void* w_qkv, int64_t ldw, int T, int H, int dtype,

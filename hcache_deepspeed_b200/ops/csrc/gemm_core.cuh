@@ -27,10 +27,10 @@ enum GemmEpilogue : int {
     EPI_QKV_ROPE = 4,   // forward QKV: Q (RoPE) to a dense buffer, K (RoPE) / V into paged KV blocks
 };
 
+constexpr int kMaxPeers = 8;
 constexpr int kGemmBM = 128;
 constexpr int kGemmBK = 64;
 constexpr int kGemmThreads = 192;
-constexpr int kMaxPeers = 8;
 
 // Pipeline depth: as many (A, W) stages as fit in ~200 KB, at most 16. `am` is the number of A rows kept in
 // shared memory: 128 normally; 16 / 64 for decode-size M, where the TMA box only delivers the live rows and
@@ -49,8 +49,18 @@ __host__ __device__ constexpr size_t gemm_smem_bytes(int bn, int am = 128) {
     return static_cast<size_t>(gemm_stages(bn, am)) * (am * kGemmBK * 2 + bn * kGemmBK * 2) + 512 + 1024;
 }
 
+// Activation operand spread over tensor-parallel peers: map i describes rows [i * rows_per_peer, ...) as they sit
+// in rank i's buffer (a peer mapping of symmetric memory). The TMA producer picks the map from the tile's row
+// range, so the all-gather of the operand happens inside the GEMM: tiles stream straight out of peer HBM over
+// NVLink / NVSwitch into shared memory, no gathered copy is ever materialised.
+struct TmapSet {
+    CUtensorMap m[kMaxPeers];
+};
+
 struct GemmArgs {
     int M, N, K;
+    int a_peers;           // > 0: A rows are sharded over this many peers (TmapSet), rows_per_peer multiple of 128
+    int a_rows_per_peer;
     int splits;            // split-K factor (>=1, no empty split)
     int kb_per_split;      // k-blocks (of 64) per split
     uint32_t a_tx_bytes;   // bytes delivered by one A box (box rows * 128)
@@ -352,7 +362,7 @@ __device__ __forceinline__ void epilogue_kv_rope(const GemmArgs& a, uint32_t tad
 template <int BN, int EPI, bool kBf16, int HD = 128, int AM = 128>
 __global__ void __launch_bounds__(kGemmThreads, 1)
 gemm_tn_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_w,
-               const GemmArgs args) {
+               const GemmArgs args, const __grid_constant__ TmapSet a_peer_maps) {
     constexpr int STAGES = gemm_stages(BN, AM);
     constexpr uint32_t A_BYTES = AM * kGemmBK * 2;
     static_assert(AM == 128 || static_cast<uint32_t>(STAGES) * BN * kGemmBK * 2 >= 16384,
@@ -424,9 +434,16 @@ gemm_tn_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
                     mbar_wait(&empty_bar[stage], phase ^ 1);
                     mbar_expect_tx(&full_bar[stage], ((args.debug_skip & 1) ? 0u : args.a_tx_bytes) + W_BYTES);
                     // activations are re-read by every n-tile: keep them in L2; weights stream once per m-wave
-                    if (!(args.debug_skip & 1))
-                        tma_load_2d(smem_a + stage * A_BYTES, &tmap_a, &full_bar[stage], kb * kGemmBK, m_t * kGemmBM,
-                                    kEvictLast);
+                    if (!(args.debug_skip & 1)) {
+                        const CUtensorMap* ta = &tmap_a;
+                        int a_row = m_t * kGemmBM;
+                        if (args.a_peers > 0) {
+                            const int peer = a_row / args.a_rows_per_peer;
+                            ta = &a_peer_maps.m[peer];
+                            a_row -= peer * args.a_rows_per_peer;
+                        }
+                        tma_load_2d(smem_a + stage * A_BYTES, ta, &full_bar[stage], kb * kGemmBK, a_row, kEvictLast);
+                    }
                     if (args.w_tiled)
                         tma_load_3d(smem_w + stage * W_BYTES, &tmap_w, &full_bar[stage], 0, kb * 32, n_t * (BN / 32),
                                     m_tiles > 1 ? kEvictNormal : kEvictFirst);

@@ -172,6 +172,22 @@ def restore_kv_proj(latents: torch.Tensor, w_kv: torch.Tensor, kv_cache_layer: t
     _count()
 
 
+def restore_kv_proj_peers(peer_ptrs: Sequence[int], rows_per_peer: int, T: int, H: int, dtype: torch.dtype, w_kv,
+                          kv_cache_layer: torch.Tensor, tok_pos: torch.Tensor, tok_slot: torch.Tensor,
+                          inv_freq: Optional[torch.Tensor], n_kv_heads: int, head_dim: int, block_size: int,
+                          bias_kv: Optional[torch.Tensor] = None) -> None:
+    """TP restore: latents row-sharded over peers' symmetric buffers, gathered by the kernel's TMA loads."""
+    arr = (ctypes.c_void_p * len(peer_ptrs))(*peer_ptrs)
+    wp, ldw = _w(w_kv)
+    lib = native.cuda_lib()
+    rc = lib.hds_restore_kv_proj_peers(arr, len(peer_ptrs), rows_per_peer, H, wp, ldw, T, H,
+                                       0 if dtype == torch.bfloat16 else 1, _p(bias_kv), _p(kv_cache_layer), _p(tok_pos),
+                                       _p(tok_slot), _p(inv_freq), n_kv_heads, head_dim, block_size,
+                                       0 if inv_freq is None else 1, _stream())
+    native.check(rc, "hds_restore_kv_proj_peers")
+    _count()
+
+
 def qkv_rope_proj(x: torch.Tensor, w_qkv: torch.Tensor, q_out: torch.Tensor, kv_cache_layer: torch.Tensor,
                   tok_pos: torch.Tensor, tok_slot: torch.Tensor, inv_freq: Optional[torch.Tensor], n_q_heads: int,
                   n_kv_heads: int, head_dim: int, block_size: int, bias_qkv: Optional[torch.Tensor] = None) -> None:

@@ -62,11 +62,35 @@ class FusedTPComm(TPComm):
                     f"({'NVLS multicast' if self.use_multicast else 'P2P atomics'})")
         return out
 
+    def alloc_symmetric(self, shape, dtype: torch.dtype) -> torch.Tensor:
+        """A zeroed tensor in symmetric memory (peers can address it: see :meth:`peer_ptrs_raw`)."""
+        t = self._symm.empty(tuple(shape), dtype=dtype, device=self.device)
+        hdl = self._symm.rendezvous(t, group=self._group_name)
+        t.zero_()
+        self._bufs.append(t)
+        self._handles.append(hdl)
+        torch.cuda.synchronize(self.device)
+        hdl.barrier(channel=0)
+        return t
+
+    def peer_ptrs_raw(self, t: torch.Tensor, byte_offset: int = 0) -> List[int]:
+        """Address of ``t`` (+offset) in every rank's copy of its symmetric allocation, this rank's mapping."""
+        base = t.data_ptr()
+        for buf, hdl in zip(self._bufs, self._handles):
+            b0 = buf.data_ptr()
+            if b0 <= base < b0 + buf.numel() * buf.element_size():
+                return [int(p) + (base - b0) + byte_offset for p in hdl.buffer_ptrs]
+        raise ValueError("tensor is not a symmetric allocation of this communicator")
+
+    def barrier(self) -> None:
+        """Device-side barrier of the TP group on the current stream (flags in symmetric memory)."""
+        self._handles[0].barrier(channel=1)
+
     def _find(self, t: torch.Tensor):
         base = t.data_ptr()
         for buf, hdl in zip(self._bufs, self._handles):
             b0 = buf.data_ptr()
-            if b0 <= base < b0 + buf.numel() * 4:
+            if b0 <= base < b0 + buf.numel() * buf.element_size():
                 return hdl, base - b0
         raise ValueError("tensor is not part of the symmetric reduction buffers")
 

@@ -57,6 +57,18 @@ int hds_restore_kv_proj(const void* latents, int64_t ld_latents, const void* w_k
                         const int32_t* tok_slot, const float* inv_freq, int n_kv_heads, int head_dim, int block_size,
                         int do_rope, void* stream);
 
+/* Tensor-parallel restore with the hidden-state all-gather fused into the projection: rank p holds rows
+ * [p*rows_per_peer, (p+1)*rows_per_peer) of the latents in ITS memory (latent_ptrs[p] = that buffer as mapped in the
+ * calling process: symmetric memory / CUDA IPC / cuMemMap peer mapping). The kernel's TMA producer reads every tile
+ * straight from the owning peer over NVLink; each rank projects all T tokens onto its own KV heads.
+ * latent_ptrs is a HOST array; rows_per_peer is a multiple of 128. The caller orders the launch after every peer's
+ * buffer is filled (device barrier). Ref: SURVEY 2.8 "(new) restore under TP" — absent in the reference. */
+int hds_restore_kv_proj_peers(const void* const* latent_ptrs, int n_peers, int rows_per_peer, int64_t ld_latents,
+                              const void* w_kv, int64_t ldw, int T, int H, int dtype, const void* bias_kv,
+                              void* kv_cache_layer, const int32_t* tok_pos, const int32_t* tok_slot,
+                              const float* inv_freq, int n_kv_heads, int head_dim, int block_size, int do_rope,
+                              void* stream);
+
 /* Forward QKV projection with the same fused epilogue: Q (RoPE) -> q_out[T, n_q*d]; K (RoPE), V -> paged cache.
  * w_qkv rows: Q heads, K heads, V heads. */
 int hds_qkv_rope_proj(const void* x, int64_t ldx, const void* w_qkv, int64_t ldw, int T, int H, int dtype,

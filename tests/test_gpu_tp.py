@@ -68,6 +68,15 @@ def _rank_fn(rank, world, arch_kwargs, fused, seed):
     probe = torch.randint(0, spec.vocab, (9, ), generator=g)
     lb, _ = eng.put([7], [probe], capture_latents=False)
     outs.append(lb.float().cpu())
+    if used_fused:
+        # sharded restore: every rank passes only its row slice; the projection kernels gather over NVLink
+        lo, hi = eng.latent_row_range(int(a.numel()))
+        mine = lat_a[:, lo:hi].contiguous().pin_memory()
+        for defer in (False, True):
+            uid = 20 + int(defer)
+            eng.restore_kv([uid], [a], [mine], sharded=True, defer=defer)
+            lc, _ = eng.put([uid], [probe], capture_latents=False)
+            torch.testing.assert_close(lc.float().cpu(), outs[-1], rtol=0, atol=0)
     torch.cuda.synchronize()
     return outs, used_fused
 
