@@ -108,7 +108,7 @@ def run_ours(a):
                        "max_ragged_sequence_count": max(B, 8), "max_context": max_ctx,
                        "memory_config": {"mode": "allocate",
                                          "size": int((B + 1) * (max_ctx + 128) * spec.kv_bytes_per_token_layer() * spec.n_layers / world)}},
-        hcache={"enabled": True, "capture": "off"})
+        hcache={"enabled": True, "capture": "off", "shard_capture": world > 1})
     eng = build_engine_from_arch(spec, cfg, seed=1234, dtype=torch.bfloat16, device=dev)
     model = eng.model()
     assert native.cuda_lib_loaded(), "sm_100a kernel library was not loaded"
@@ -139,7 +139,14 @@ def run_ours(a):
     hidden_layers, recompute_layers = plan.layers_of("hidden"), plan.layers_of("none")
     lat_hidden = latents[hidden_layers[0]:] if hidden_layers else None  # the plan keeps a suffix of layers
     interleave = plan.interleave
-    h2d_step = B * (len(hidden_layers) * ctx * spec.hidden * 2 + ctx * 4 + n_new * 4) + B * D * 4
+    # tensor parallel: every rank keeps (and transfers) only its 1/tp row slice of the hidden states; the restore
+    # kernels gather the slices from peer HBM over NVLink (needs the fused/symmetric-memory communicator)
+    sharded = world > 1 and bool(getattr(model.comm, "fused", False))
+    if sharded:
+        lo, hi = eng.latent_row_range(ctx)
+        lat_slice = latents[:, lo:hi].contiguous().pin_memory()
+    rows_moved = (hi - lo) if sharded else ctx
+    h2d_step = B * (len(hidden_layers) * rows_moved * spec.hidden * 2 + ctx * 4 + n_new * 4) + B * D * 4
     d2h_step = B * (D + 1) * 4
 
     ev = lambda: torch.cuda.Event(enable_timing=True)  # noqa: E731
@@ -152,8 +159,11 @@ def run_ours(a):
         for i, uid in enumerate(uids):
             t0, e0, e1 = time.perf_counter(), ev(), ev()
             e0.record()
-            eng.restore_session(uid, ctx_tokens, hidden=lat_hidden, hidden_layers=hidden_layers,
-                                recompute_layers=recompute_layers, interleave=interleave)
+            if sharded:
+                eng.restore_kv([uid], [ctx_tokens], [lat_slice], do_checks=False, sharded=True)
+            else:
+                eng.restore_session(uid, ctx_tokens, hidden=lat_hidden, hidden_layers=hidden_layers,
+                                    recompute_layers=recompute_layers, interleave=interleave)
             logits, _ = eng.put([uid], [new_tokens[i]], do_checks=False)
             tok = kernels.argmax(logits)
             tok_host = tok.cpu()  # D2H of the first token: the TTFT point
@@ -218,8 +228,11 @@ def run_ours(a):
             "ttft_p50_ms": round(ttft_dev, 3),
             "config": {"model": a.model, "global_batch": B, "seq_len": ctx + n_new + D, "parallelism": f"tp{world}",
                        "restored_ctx": ctx, "new_turn_tokens": n_new, "decode_steps": D,
-                       "restore_plan": {"recompute_prefix_layers": len(recompute_layers), "hidden_state_layers": len(hidden_layers),
-                                        "kv_offload_layers": 0},
+                       "restore_plan": {"recompute_prefix_layers": 0 if sharded else len(recompute_layers),
+                                        "hidden_state_layers": spec.n_layers if sharded else len(hidden_layers),
+                                        "kv_offload_layers": 0, "tp_sharded_restore": sharded,
+                                        "tp_collectives": "fused GEMM-epilogue reduction" if bool(getattr(model.comm, "fused", False))
+                                        else ("nccl" if world > 1 else "none")},
                        "l2_policy": f"working set per step (weights {model.w.n_bytes() / 2**30:.1f} GiB + KV) exceeds the 126 MB L2"},
             "e2e": {"value": round(dec_tokens / (dec_host_ms / 1e3), 2), "unit": "tokens/s", "ttft_p50_ms": round(ttft_host, 3),
                     "h2d_bytes_per_step": h2d_step, "d2h_bytes_per_step": d2h_step},

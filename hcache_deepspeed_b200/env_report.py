@@ -1,0 +1,60 @@
+"""``hds_report``: environment and native-op status (ref: deepspeed/env_report.py)."""
+from __future__ import annotations
+
+import os
+import shutil
+import subprocess
+import sys
+
+GREEN, RED, YELLOW, END = "\033[92m", "\033[91m", "\033[93m", "\033[0m"
+OKAY, NO = f"{GREEN}[OKAY]{END}", f"{RED}[NO]{END}"
+
+
+def op_report(verbose: bool = True):
+    from .ops import build
+    rows = []
+    for name, path, tool in (("sm_100a kernel library (libhds_b200.so)", build.CUDA_LIB, "nvcc"),
+                             ("host runtime (libhds_host.so)", build.HOST_LIB, "g++")):
+        rows.append((name, path.exists(), shutil.which(tool) is not None or os.path.exists("/usr/local/cuda/bin/" + tool)))
+    print("-" * 74)
+    print("native op report")
+    print("-" * 74)
+    print(f"{'op name':<45}{'built':<12}{'buildable here':<12}")
+    for name, built, can in rows:
+        print(f"{name:<45}{OKAY if built else NO:<21}{OKAY if can else NO}")
+    try:
+        from .io import gds_available
+        print(f"{'GPUDirect Storage (libcufile)':<45}{OKAY if gds_available() else NO}")
+    except Exception:
+        pass
+    return rows
+
+
+def debug_report():
+    import torch
+    from . import __version__
+    nvcc = shutil.which("nvcc") or "/usr/local/cuda/bin/nvcc"
+    nvcc_ver = "n/a"
+    if os.path.exists(nvcc):
+        out = subprocess.run([nvcc, "--version"], capture_output=True, text=True).stdout
+        nvcc_ver = out.strip().splitlines()[-2] if out else "n/a"
+    rows = [("torch version", torch.__version__), ("torch cuda version", torch.version.cuda),
+            ("cuda available", torch.cuda.is_available()),
+            ("device", torch.cuda.get_device_name(0) if torch.cuda.is_available() else "cpu"),
+            ("nvcc", nvcc_ver), ("hcache_deepspeed_b200", __version__), ("python", sys.version.split()[0]),
+            ("nccl", ".".join(map(str, torch.cuda.nccl.version())) if torch.cuda.is_available() else "n/a")]
+    print("-" * 74)
+    print("general environment info")
+    print("-" * 74)
+    for k, v in rows:
+        print(f"{k:.<30} {v}")
+    return rows
+
+
+def cli_main():
+    op_report()
+    debug_report()
+
+
+if __name__ == "__main__":
+    cli_main()

@@ -70,6 +70,9 @@ class InferenceEngineV2:
         self._model.set_state_manager(self._state_manager)
         self._capture_stream = torch.cuda.Stream(device=self._model.device) if self._model.device.type == "cuda" else None
         self.last_put_stats = {}
+        self._decode_graphs = {}   # (n_seqs, attention splits) -> (CUDAGraph, static logits)
+        self._decode_warm = {}     # eager runs seen per key before capturing
+        self.graph_replays = 0
 
     # ------------------------------------------------------------------------------------------------
     def _initialize_tp_group(self):
@@ -225,7 +228,11 @@ class InferenceEngineV2:
             capture = hc.enabled and hc.capture != "off"
             if capture and not hc.capture_decode_steps and self._batch.current_tokens == self._batch.current_sequences:
                 capture = False
-        logits, latent_dev = self._model.forward(self._batch, capture=bool(capture), all_logits=all_logits)
+        if (not capture and not all_logits and self._config.use_cuda_graph_decode and self._model.device.type == "cuda"
+                and self._batch.current_tokens == self._batch.current_sequences and self._batch.n_items_large == 0):
+            logits, latent_dev = self._graphed_decode(), None
+        else:
+            logits, latent_dev = self._model.forward(self._batch, capture=bool(capture), all_logits=all_logits)
         latents = self._export_latents(latent_dev) if capture else [None] * len(uids)
         assert logits.shape[0] == (self._batch.current_tokens if all_logits else self._batch.current_sequences)
         for uid in uids:
@@ -233,6 +240,35 @@ class InferenceEngineV2:
             seq.post_forward()
             self._model.maybe_free_kv(seq)
         return logits, latents
+
+    def _graphed_decode(self) -> torch.Tensor:
+        """Pure decode step through a CUDA graph. The batch metadata (token ids, slots, block tables, work items)
+        lives in fixed device buffers refreshed by ``finalize`` before every replay; only launch geometry is baked
+        in, so one graph serves a given (sequence count, KV split count) until the heuristic wants more splits."""
+        from ...ops.backend import pick_decode_splits
+        model, batch = self._model, self._batch
+        model.finish_pending_restore()
+        key = (batch.current_sequences, pick_decode_splits(batch.n_items_small, model.n_kv, batch.max_kv_len_small),
+               batch.rows_per_small_item)
+        entry = self._decode_graphs.get(key)
+        if entry is None:
+            seen = self._decode_warm.get(key, 0)
+            self._decode_warm[key] = seen + 1
+            if seen < 2:  # first steps run eagerly (lazy kernel attribute setup, allocator warm-up)
+                return model.forward(batch, capture=False)[0]
+            torch.cuda.synchronize(model.device)
+            graph = torch.cuda.CUDAGraph()
+            side = torch.cuda.Stream(device=model.device)
+            side.wait_stream(torch.cuda.current_stream())
+            with torch.cuda.stream(side):
+                with torch.cuda.graph(graph, stream=side):
+                    static_logits = model.forward(batch, capture=False)[0]
+            torch.cuda.current_stream().wait_stream(side)
+            entry = (graph, static_logits)
+            self._decode_graphs[key] = entry
+        entry[0].replay()
+        self.graph_replays += 1
+        return entry[1]
 
     def _export_latents(self, latent_dev: torch.Tensor) -> List:
         """Device ``[L, T, H]`` -> pinned host memory, split into per-sequence views (engine_v2.py:172-179).

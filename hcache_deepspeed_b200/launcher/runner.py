@@ -1,0 +1,194 @@
+"""Job launcher front end (ref: deepspeed/launcher/runner.py + multinode_runner.py).
+
+``hds [--hostfile F] [--include ...] [--exclude ...] [--num_nodes N] [--num_gpus G] [--master_addr A]
+[--master_port P] [--launcher pdsh|ssh|local] script.py args...``
+
+Single node: spawns ``launcher.launch`` directly. Multi node: builds the per-node command line and runs it over
+pdsh / ssh with the resource map base64-encoded, exactly as the reference does. One process per GPU; ranks
+rendezvous through ``torch.distributed`` (NCCL).
+"""
+from __future__ import annotations
+
+import argparse
+import base64
+import collections
+import json
+import os
+import re
+import shlex
+import subprocess
+import sys
+from typing import Dict, List, Optional
+
+DLTS_HOSTFILE = "/job/hostfile"
+EXPORT_ENVS = ["NCCL", "PYTHON", "MV2", "UCX", "HDS", "CUDA"]
+PDSH_MAX_FAN_OUT = 1024
+
+
+def parse_args(args=None):
+    p = argparse.ArgumentParser(description="hcache_deepspeed_b200 runner: launch one process per GPU on one or more nodes")
+    p.add_argument("-H", "--hostfile", type=str, default=DLTS_HOSTFILE)
+    p.add_argument("-i", "--include", type=str, default="")
+    p.add_argument("-e", "--exclude", type=str, default="")
+    p.add_argument("--num_nodes", type=int, default=-1)
+    p.add_argument("--min_elastic_nodes", type=int, default=-1)
+    p.add_argument("--max_elastic_nodes", type=int, default=-1)
+    p.add_argument("--num_gpus", "--num_accelerators", type=int, default=-1)
+    p.add_argument("--master_port", default=29500, type=int)
+    p.add_argument("--master_addr", default="", type=str)
+    p.add_argument("--launcher", default="pdsh", type=str, help="pdsh | ssh | local")
+    p.add_argument("--launcher_args", default="", type=str)
+    p.add_argument("--module", action="store_true")
+    p.add_argument("--no_python", action="store_true")
+    p.add_argument("--no_local_rank", action="store_true")
+    p.add_argument("--no_ssh_check", action="store_true")
+    p.add_argument("--force_multi", action="store_true")
+    p.add_argument("--save_pid", action="store_true")
+    p.add_argument("--enable_each_rank_log", default="None", type=str)
+    p.add_argument("--bind_cores_to_rank", action="store_true")
+    p.add_argument("--elastic_training", action="store_true")
+    p.add_argument("user_script", type=str)
+    p.add_argument("user_args", nargs=argparse.REMAINDER)
+    return p.parse_args(args=args)
+
+
+def fetch_hostfile(hostfile_path: str) -> Optional["collections.OrderedDict[str, int]"]:
+    if not os.path.isfile(hostfile_path):
+        return None
+    with open(hostfile_path) as fd:
+        return _parse_hostfile(fd.readlines())
+
+
+def _parse_hostfile(lines: List[str]) -> "collections.OrderedDict[str, int]":
+    pattern = r"^(\S+)\s+slots=(\d+)"
+    pool = collections.OrderedDict()
+    for line in lines:
+        line = line.strip()
+        if not line or line.startswith("#"):
+            continue
+        m = re.search(pattern, line)
+        if not m:
+            raise ValueError(f"Hostfile contains a bad entry: {line}, unable to proceed with launching")
+        host, slots = m.group(1), int(m.group(2))
+        if host in pool:
+            raise ValueError(f"Hostfile contains multiple entries for {host}, unable to proceed with launching")
+        pool[host] = slots
+    if not pool:
+        raise ValueError("Hostfile is empty or not formatted correctly, unable to proceed with launching.")
+    return pool
+
+
+def parse_resource_filter(host_info: Dict[str, List[int]], include_str: str = "", exclude_str: str = "") -> Dict[str, List[int]]:
+    """``host1@host2:0,2`` style include / exclude filters (mutually exclusive), as in the reference."""
+    if include_str and exclude_str:
+        raise ValueError("include_str and exclude_str are mutually exclusive.")
+    if not include_str and not exclude_str:
+        return host_info
+    filtered: Dict[str, List[int]] = {}
+    parse_str = include_str or exclude_str
+    if exclude_str:
+        filtered = {h: list(s) for h, s in host_info.items()}
+    for node_config in parse_str.split("@"):
+        if ":" in node_config:
+            hostname, slots = node_config.split(":")
+            slots = [int(x) for x in slots.split(",")]
+            if hostname not in host_info:
+                raise ValueError(f"Hostname '{hostname}' not found in hostfile")
+            for s in slots:
+                if s not in host_info[hostname]:
+                    raise ValueError(f"No slot '{s}' specified on host '{hostname}'")
+            if include_str:
+                filtered.setdefault(hostname, [])
+                filtered[hostname] += slots
+            else:
+                for s in slots:
+                    filtered[hostname].remove(s)
+        else:
+            hostname = node_config
+            if hostname not in host_info:
+                raise ValueError(f"Hostname '{hostname}' not found in hostfile")
+            if include_str:
+                filtered[hostname] = list(host_info[hostname])
+            else:
+                filtered[hostname] = []
+    filtered = {h: sorted(set(s)) for h, s in filtered.items() if s}
+    ordered = collections.OrderedDict()
+    for host in host_info:
+        if host in filtered:
+            ordered[host] = filtered[host]
+    return ordered
+
+
+def parse_inclusion_exclusion(resource_pool, inclusion: str, exclusion: str):
+    active = collections.OrderedDict((h, list(range(s))) for h, s in resource_pool.items())
+    return parse_resource_filter(active, include_str=inclusion, exclude_str=exclusion)
+
+
+def encode_world_info(world_info) -> str:
+    return base64.urlsafe_b64encode(json.dumps(world_info).encode()).decode()
+
+
+def build_launch_cmd(args, world_info_b64: str, node_rank: str = "%n") -> List[str]:
+    cmd = [sys.executable, "-u", "-m", "hcache_deepspeed_b200.launcher.launch", f"--world_info={world_info_b64}",
+           f"--node_rank={node_rank}", f"--master_addr={args.master_addr}", f"--master_port={args.master_port}"]
+    if args.no_python:
+        cmd.append("--no_python")
+    if args.module:
+        cmd.append("--module")
+    if args.no_local_rank:
+        cmd.append("--no_local_rank")
+    if args.save_pid:
+        cmd += ["--save_pid", str(os.getpid())]
+    if args.enable_each_rank_log != "None":
+        cmd.append(f"--enable_each_rank_log={args.enable_each_rank_log}")
+    return cmd + [args.user_script] + list(args.user_args)
+
+
+def build_multinode_cmd(args, active_resources, world_info_b64: str, env: Dict[str, str]) -> List[str]:
+    exports = " ".join(f"export {k}={shlex.quote(v)};" for k, v in env.items() if any(k.startswith(p) for p in EXPORT_ENVS))
+    if args.launcher == "pdsh":
+        hosts = ",".join(active_resources.keys())
+        launch = build_launch_cmd(args, world_info_b64, node_rank="%n")
+        return ["pdsh", "-S", "-f", str(PDSH_MAX_FAN_OUT), "-w", hosts] + shlex.split(args.launcher_args) + \
+            [exports + f" cd {os.path.abspath('.')}; " + " ".join(map(shlex.quote, launch))]
+    if args.launcher == "ssh":
+        script = []
+        for rank, host in enumerate(active_resources):
+            launch = build_launch_cmd(args, world_info_b64, node_rank=str(rank))
+            script.append(f"ssh {shlex.quote(host)} {shlex.quote(exports + ' cd ' + os.path.abspath('.') + '; ' + ' '.join(map(shlex.quote, launch)))} &")
+        return ["bash", "-c", "\n".join(script) + "\nwait"]
+    raise NotImplementedError(f"Unknown launcher {args.launcher}")
+
+
+def main(args=None):
+    args = parse_args(args)
+    resource_pool = fetch_hostfile(args.hostfile)
+    if not resource_pool:
+        import torch
+        n = args.num_gpus if args.num_gpus > 0 else max(1, torch.cuda.device_count())
+        resource_pool = collections.OrderedDict(localhost=n)
+        args.master_addr = args.master_addr or "127.0.0.1"
+    active = parse_inclusion_exclusion(resource_pool, args.include, args.exclude)
+    if args.num_nodes > 0:
+        active = collections.OrderedDict(list(active.items())[:args.num_nodes])
+    if args.num_gpus > 0:
+        active = collections.OrderedDict((h, s[:args.num_gpus]) for h, s in active.items())
+    multi_node = args.force_multi or len(active) > 1
+    if not args.master_addr:
+        first = next(iter(active))
+        args.master_addr = "127.0.0.1" if not multi_node else \
+            subprocess.check_output(["ssh", first, "hostname -I"]).decode().split()[0]
+    world_info = encode_world_info(active)
+    env = os.environ.copy()
+    if not multi_node:
+        cmd = build_launch_cmd(args, world_info, node_rank="0")
+    else:
+        cmd = build_multinode_cmd(args, active, world_info, env)
+    result = subprocess.Popen(cmd, env=env)
+    result.wait()
+    if result.returncode != 0:
+        sys.exit(result.returncode)
+
+
+if __name__ == "__main__":
+    main()

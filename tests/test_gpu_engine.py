@@ -83,6 +83,32 @@ def test_deferred_restore_overlaps_next_put():
     torch.cuda.synchronize()
 
 
+def test_cuda_graph_decode_matches_eager():
+    from hcache_deepspeed_b200.inference.v2 import RaggedInferenceEngineConfig, build_engine_from_arch
+    from hcache_deepspeed_b200.models.arch import named_arch
+    spec = named_arch("llama-2-7b").scaled(n_layers=2)
+    engines = []
+    for graphs in (False, True):
+        cfg = _cfg(T=512, ctx=2048, mem=1 << 30)
+        cfg.use_cuda_graph_decode = graphs
+        engines.append(build_engine_from_arch(spec, cfg, seed=9, device=torch.device("cuda")))
+    g = torch.Generator().manual_seed(2)
+    prompts = [torch.randint(0, spec.vocab, (n, ), generator=g) for n in (100, 37, 260)]
+    outs = []
+    for eng in engines:
+        lg, _ = eng.put([1, 2, 3], prompts, capture_latents=False)
+        seq = [lg.float().cpu()]
+        cur = lg.argmax(-1).cpu()
+        for _ in range(8):  # crosses a KV block boundary and several graph replays
+            lg, _ = eng.put([1, 2, 3], [cur[i:i + 1] for i in range(3)], capture_latents=False)
+            seq.append(lg.float().cpu().clone())
+            cur = lg.argmax(-1).cpu()
+        outs.append(seq)
+    assert engines[1].graph_replays >= 5 and engines[0].graph_replays == 0
+    for a, b in zip(*outs):
+        torch.testing.assert_close(a, b, rtol=0, atol=0)
+
+
 def test_async_capture_and_flush():
     from hcache_deepspeed_b200.inference.v2 import LatentHandle, build_engine_from_arch
     eng = build_engine_from_arch("tiny-llama-test", _cfg(enabled=True, capture="async"), seed=2, device=torch.device("cuda"))
