@@ -1,0 +1,2 @@
+from .elasticity import (ElasticityConfig, ElasticityConfigError, ElasticityError, ElasticityIncompatibleWorldSize,  # noqa: F401
+                         compute_elastic_config, elasticity_enabled, get_compatible_gpus)
