@@ -52,6 +52,7 @@ def shard_rows(n_tokens: int, tp_size: int, tp_rank: int) -> Tuple[int, int, int
 class TPComm:
     """How row-parallel partial sums meet across tensor-parallel ranks (see parallel/tp_comm.py)."""
     fused = False
+    mode = "nccl"
 
     def __init__(self, group=None, size: int = 1, rank: int = 0):
         self.group, self.size, self.rank = group, size, rank
@@ -195,7 +196,11 @@ class RaggedTransformer:
             self.restore_stage_sym = None
             if self.tp_size > 1 and getattr(self.comm, "fused", False):
                 # per-rank slice of the staging ring in symmetric memory: peers' restore kernels read it over NVLink
-                self._sym_rows = ceil_div(ceil_div(T, self.tp_size), 128) * 128
+                # "copy" gather: full-size slots, each rank fills its own rows and pulls the peers' rows (one P2P read of
+                # every byte); "kernel" gather: per-rank slices that the projection kernel reads through peer tensor maps
+                import os
+                self.tp_gather = os.environ.get("HDS_TP_GATHER", "copy")
+                self._sym_rows = T if self.tp_gather == "copy" else ceil_div(ceil_div(T, self.tp_size), 128) * 128
                 self.restore_stage_sym = self.comm.alloc_symmetric((RESTORE_SLOTS, self._sym_rows, H), dt)
             self.restore_pos = torch.zeros(T, dtype=torch.int32, device=dev)
             self.restore_slot = torch.zeros(T, dtype=torch.int32, device=dev)
@@ -250,6 +255,21 @@ class RaggedTransformer:
     # ------------------------------------------------------------------------------------------------
     # forward
     # ------------------------------------------------------------------------------------------------
+    def _norm(self, x, gamma, out, beta=None, delta=None, res_out=None) -> torch.Tensor:
+        """Norm that folds the pending delta into the residual stream. Under fused (pull) tensor parallelism the fp32
+        delta is the sum of every rank's buffer, read over NVLink inside the kernel, and the other buffer of the
+        alternating pair is cleared for the next reducing GEMM."""
+        s = self.spec
+        zero_buf = None
+        comm = None
+        if (delta is not None and delta.dtype == torch.float32 and self.tp_size > 1 and getattr(self.comm, "fused", False)
+                and self.comm.mode == "pull"):
+            comm = self.comm
+            i = 0 if delta.data_ptr() == self._delta_bufs[0].data_ptr() else 1
+            zero_buf = self._delta_bufs[1 - i][:delta.shape[0]]
+        return self.ops.norm(x, gamma, out, beta=beta, delta=delta, zero_delta=comm is None, res_out=res_out,
+                             eps=s.norm_eps, layer_norm=s.norm == "layer", comm=comm, zero_buf=zero_buf)
+
     def _row_parallel(self, x: torch.Tensor, w: torch.Tensor, b: Optional[torch.Tensor], T: int, force_accum: bool,
                       last_into_delta: bool = True) -> torch.Tensor:
         """y = x @ w.T (+b), left as the pending delta. fp32 partial sums when the GEMM is split over K or ranks."""
@@ -307,11 +327,11 @@ class RaggedTransformer:
             g = torch.sigmoid(ref.gemm(x, lw.w_shared_gate, out_dtype=torch.float32))
             d32 += ys.float() * g
         if self.tp_size > 1:
-            if getattr(self.comm, "fused", False):
+            if getattr(self.comm, "fused", False) and self.comm.mode == "push":
                 import torch.distributed as dist
-                dist.all_reduce(d32, group=self.comm.group)  # MoE partials are added locally: plain all-reduce
+                dist.all_reduce(d32, group=self.comm.group)  # MoE partials were added locally: plain all-reduce
             else:
-                self.comm.all_reduce_delta(d32)
+                self.comm.all_reduce_delta(d32)  # NCCL all-reduce, or (pull mode) just the barrier
         self._delta_idx = (self._delta_idx + 1) % len(self._delta_bufs)
         return d32
 
@@ -341,8 +361,8 @@ class RaggedTransformer:
         for li in range(n_run):
             lw = w.layers[li]
             xn = (self.latent_buf[li] if capture else self.xn)[:T]
-            ops.norm(resid, lw.norm1_g, xn, beta=lw.norm1_b, delta=pending, zero_delta=True,
-                     res_out=resid if pending is not None else None, eps=s.norm_eps, layer_norm=ln)
+            self._norm(resid, lw.norm1_g, xn, beta=lw.norm1_b, delta=pending,
+                       res_out=resid if pending is not None else None)
             kv_layer = kv.get_cache(li)
             if self._pending_restore is not None:
                 self._restore_step(li)  # deferred HCache restore: this layer's K/V must land before its attention
@@ -354,13 +374,12 @@ class RaggedTransformer:
             if s.parallel_residual:
                 xm = xn
                 if two_norms:
-                    xm = ops.norm(resid, lw.norm2_g, self.xn2[:T], beta=lw.norm2_b, eps=s.norm_eps, layer_norm=ln)
+                    xm = self._norm(resid, lw.norm2_g, self.xn2[:T], beta=lw.norm2_b)
                 self._row_parallel(attn, lw.w_o, lw.b_o, T, force_accum=True, last_into_delta=False)
                 pending = self._mlp(xm, lw, T, force_accum=True)
             else:
                 d1 = self._row_parallel(attn, lw.w_o, lw.b_o, T, force_accum=False)
-                x2 = ops.norm(resid, lw.norm2_g, self.xn2[:T], beta=lw.norm2_b, delta=d1, zero_delta=True, res_out=resid,
-                              eps=s.norm_eps, layer_norm=ln)
+                x2 = self._norm(resid, lw.norm2_g, self.xn2[:T], beta=lw.norm2_b, delta=d1, res_out=resid)
                 pending = self._mlp(x2, lw, T, force_accum=False)
             if n_layers_limit is not None and restore_interleave > 0 and self._pending_restore is not None:
                 st = self._pending_restore
@@ -371,15 +390,18 @@ class RaggedTransformer:
                     self._pending_restore = None
         if n_layers_limit is not None:
             if pending is not None and pending.dtype == torch.float32:
-                pending.zero_()  # the partial sums of the last executed layer are not consumed by a norm
+                # the partial sums of the last executed layer are not consumed by a norm; under pull-mode TP the
+                # previously consumed buffer is still dirty as well (every rank is past the barrier that follows
+                # the last GEMM, so nobody reads either buffer any more)
+                for b in self._delta_bufs:
+                    b[:T].zero_()
             return None, (self.latent_buf[:n_run, :T] if capture else None)
         if self._pending_restore is not None:
             self.finish_pending_restore()
         # ---- last-token logits ----
         fin = self.xn2[:T]
         if s.final_norm:
-            ops.norm(resid, w.final_norm_g, fin, beta=w.final_norm_b, delta=pending, zero_delta=True, eps=s.norm_eps,
-                     layer_norm=ln)
+            self._norm(resid, w.final_norm_g, fin, beta=w.final_norm_b, delta=pending)
         else:
             ones = torch.ones(s.hidden, dtype=self.dtype, device=self.device)
             ops.norm(resid, ones, self.xn[:T], delta=pending, zero_delta=True, res_out=fin, eps=s.norm_eps)
@@ -468,6 +490,8 @@ class RaggedTransformer:
             if i >= RESTORE_SLOTS:
                 io.wait_event(self.ev_consumed[k])
             off = 0
+            if st["sharded"] and self.tp_gather == "copy":
+                off = shard_rows(st["T"], self.tp_size, self.tp_rank)[0]  # my rows sit at their global position
             for lat in st["latents"]:
                 n = int(lat.shape[1])
                 stage[off:off + n].copy_(lat[i], non_blocking=True)
@@ -488,11 +512,25 @@ class RaggedTransformer:
             # every rank's slice of this layer has landed in its own HBM -> gather inside the projection kernel
             _, _, per = shard_rows(T, self.tp_size, self.tp_rank)
             self.comm.barrier()
-            ptrs = self.comm.peer_ptrs_raw(self.restore_stage_sym, byte_offset=k * self._sym_rows * s.hidden * 2)
-            self.ops.k.restore_kv_proj_peers(ptrs, per, T, s.hidden, self.dtype, wk, kv.get_cache(li), self.restore_pos[:T],
-                                             self.restore_slot[:T], self.inv_freq, self.n_kv, self.d, kv.kv_block_size,
-                                             bias_kv=bk)
-            self.comm.barrier()  # peers are done reading my slot before it is refilled
+            if self.tp_gather == "copy":
+                # pull every peer's rows once over NVLink into my full-size slot, then project locally
+                slot_t = self.restore_stage_sym[k]
+                for p in range(self.tp_size):
+                    if p == self.tp_rank:
+                        continue
+                    lo_p, hi_p, _ = shard_rows(T, self.tp_size, p)
+                    if hi_p > lo_p:
+                        slot_t[lo_p:hi_p].copy_(self.comm.peer_view(slot_t[lo_p:hi_p], p), non_blocking=True)
+                self.comm.barrier()  # peers have read my rows: the slot may be refilled once my kernel is done
+                self.ops.restore_kv_proj(slot_t[:T], wk, bk, kv.get_cache(li), self.restore_pos[:T], self.restore_slot[:T],
+                                         self.inv_freq, self.n_kv, self.d, s.rot_dim, kv.kv_block_size,
+                                         scratch=self.kv_scratch[:T] if self.kv_scratch is not None else None)
+            else:
+                ptrs = self.comm.peer_ptrs_raw(self.restore_stage_sym, byte_offset=k * self._sym_rows * s.hidden * 2)
+                self.ops.k.restore_kv_proj_peers(ptrs, per, T, s.hidden, self.dtype, wk, kv.get_cache(li),
+                                                 self.restore_pos[:T], self.restore_slot[:T], self.inv_freq, self.n_kv,
+                                                 self.d, kv.kv_block_size, bias_kv=bk)
+                self.comm.barrier()  # peers are done reading my slot before it is refilled
         else:
             self.ops.restore_kv_proj(self.restore_stage[k][:T], wk, bk, kv.get_cache(li), self.restore_pos[:T],
                                      self.restore_slot[:T], self.inv_freq, self.n_kv, self.d, s.rot_dim, kv.kv_block_size,

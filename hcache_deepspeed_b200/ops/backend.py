@@ -29,7 +29,8 @@ class CpuOps:
         accum += ref.gemm(a, w, bias=bias, out_dtype=torch.float32)
 
     # ---- norm -----------------------------------------------------------------------------------
-    def norm(self, x, gamma, out, beta=None, delta=None, zero_delta=False, res_out=None, eps=1e-5, layer_norm=False):
+    def norm(self, x, gamma, out, beta=None, delta=None, zero_delta=False, res_out=None, eps=1e-5, layer_norm=False,
+             comm=None, zero_buf=None):
         if delta is not None:
             s = (x.float() + delta.float()).to(x.dtype)
             if zero_delta and delta.dtype == torch.float32:
@@ -98,12 +99,18 @@ class CudaOps:
                            workspace=workspace if a.shape[0] <= 128 else None)
 
     def gemm_accum(self, a, w, accum, bias=None, comm=None):
-        if comm is not None and comm.fused:
+        if comm is not None and comm.fused and comm.mode == "push":
+            # GEMM -> all-reduce in the epilogue: reduce the tile into every rank's buffer (NVLS multicast / P2P red)
             self.k.gemm_accum(a, w, accum, bias=bias, peer_ptrs=comm.peer_ptrs(accum), multicast_ptr=comm.multicast_ptr(accum))
         else:
             self.k.gemm_accum(a, w, accum, bias=bias)
 
-    def norm(self, x, gamma, out, beta=None, delta=None, zero_delta=False, res_out=None, eps=1e-5, layer_norm=False):
+    def norm(self, x, gamma, out, beta=None, delta=None, zero_delta=False, res_out=None, eps=1e-5, layer_norm=False,
+             comm=None, zero_buf=None):
+        if comm is not None and comm.fused and comm.mode == "pull" and delta is not None and delta.dtype == torch.float32:
+            # pull all-reduce fused into the norm: sum every rank's partial-sum buffer over NVLink
+            return self.k.norm_tp(x, gamma, out, comm.peer_ptrs_raw(delta), zero_buf=zero_buf, beta=beta, res_out=res_out,
+                                  eps=eps, layer_norm=layer_norm)
         return self.k.norm(x, gamma, out, beta=beta, delta=delta, zero_delta=zero_delta, res_out=res_out, eps=eps,
                            layer_norm=layer_norm)
 

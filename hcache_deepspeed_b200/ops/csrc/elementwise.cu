@@ -32,11 +32,20 @@ __device__ __forceinline__ float block_sum_256(float v, float* red) {
 //               are cleared after being read so the next accumulating GEMM starts from zero.
 //   res_out   : optional, receives x_in + delta (pre-norm) or the normalised value (post_norm)
 //   out       : normalised output;  row_idx: optional gather of input rows (last-token gather)
+// Tensor-parallel pull reduction: the fp32 partial sums of a row-parallel GEMM stay in each rank's own buffer
+// (symmetric memory); the consuming norm kernel adds up all ranks' copies with plain loads over NVLink — no remote
+// atomics, no NCCL kernel — and clears the OTHER buffer of the alternating pair for the next reducing GEMM.
+struct DeltaPeers {
+    const float* src[8];  // same buffer on every rank (this rank's mapping of each), src[0..n)
+    int n;                // 0 = single local delta (the `delta` argument)
+    float* zero_buf;      // local buffer to clear (rows x cols fp32), may be null
+};
+
 template <int VPT, bool kBf16, bool kLayerNorm, bool kDeltaF32>
 __global__ void __launch_bounds__(kNormThreads)
 norm_kernel(const void* __restrict__ x_in, void* delta, void* res_out, void* __restrict__ out,
             const void* __restrict__ gamma, const void* __restrict__ beta, const int32_t* __restrict__ row_idx,
-            int cols, float eps, int zero_delta, int post_norm, int64_t ld_in, int64_t ld_out) {
+            int cols, float eps, int zero_delta, int post_norm, int64_t ld_in, int64_t ld_out, const DeltaPeers peers) {
     __shared__ float red[kNormThreads / 32];
     const int r_out = blockIdx.x;
     const int r_in = row_idx ? row_idx[r_out] : r_out;
@@ -53,7 +62,26 @@ norm_kernel(const void* __restrict__ x_in, void* delta, void* res_out, void* __r
             v[i][2] = unpack_lo<kBf16>(q.y); v[i][3] = unpack_hi<kBf16>(q.y);
             v[i][4] = unpack_lo<kBf16>(q.z); v[i][5] = unpack_hi<kBf16>(q.z);
             v[i][6] = unpack_lo<kBf16>(q.w); v[i][7] = unpack_hi<kBf16>(q.w);
-            if (delta != nullptr) {
+            if (kDeltaF32 && peers.n > 0) {
+                const int64_t off = static_cast<int64_t>(r_in) * cols + vi * 8;
+                for (int s = 0; s < peers.n; ++s) {
+                    const float4* dp = reinterpret_cast<const float4*>(peers.src[s] + off);
+                    const float4 d0 = dp[0], d1 = dp[1];
+                    v[i][0] += d0.x; v[i][1] += d0.y; v[i][2] += d0.z; v[i][3] += d0.w;
+                    v[i][4] += d1.x; v[i][5] += d1.y; v[i][6] += d1.z; v[i][7] += d1.w;
+                }
+                if (peers.zero_buf != nullptr) {
+                    float4* zp = reinterpret_cast<float4*>(peers.zero_buf + off);
+                    zp[0] = make_float4(0.f, 0.f, 0.f, 0.f);
+                    zp[1] = make_float4(0.f, 0.f, 0.f, 0.f);
+                }
+#pragma unroll
+                for (int j = 0; j < 8; j += 2) {
+                    uint32_t p = pack2<kBf16>(v[i][j], v[i][j + 1]);
+                    v[i][j] = unpack_lo<kBf16>(p);
+                    v[i][j + 1] = unpack_hi<kBf16>(p);
+                }
+            } else if (delta != nullptr) {
                 if (kDeltaF32) {
                     float4* dp = reinterpret_cast<float4*>(reinterpret_cast<float*>(delta) +
                                                            static_cast<int64_t>(r_in) * cols + vi * 8);
@@ -154,13 +182,13 @@ norm_kernel(const void* __restrict__ x_in, void* delta, void* res_out, void* __r
 template <bool kBf16, bool kLayerNorm, bool kDeltaF32>
 static int launch_norm_vpt(int rows, int cols, const void* x, void* delta, void* res_out, void* out, const void* gamma,
                            const void* beta, const int32_t* row_idx, float eps, int zero_delta, int post_norm,
-                           int64_t ld_in, int64_t ld_out, cudaStream_t s) {
+                           int64_t ld_in, int64_t ld_out, const DeltaPeers& peers, cudaStream_t s) {
     const int nvec = cols / 8;
     const int vpt = (nvec + kNormThreads - 1) / kNormThreads;
 #define HDS_NORM_LAUNCH(V)                                                                                        \
     norm_kernel<V, kBf16, kLayerNorm, kDeltaF32><<<rows, kNormThreads, 0, s>>>(x, delta, res_out, out, gamma, beta, \
                                                                                row_idx, cols, eps, zero_delta,      \
-                                                                               post_norm, ld_in, ld_out)
+                                                                               post_norm, ld_in, ld_out, peers)
     if (vpt <= 1) HDS_NORM_LAUNCH(1);
     else if (vpt <= 2) HDS_NORM_LAUNCH(2);
     else if (vpt <= 4) HDS_NORM_LAUNCH(4);
@@ -368,9 +396,35 @@ __global__ void cvt_f32_kernel(float* __restrict__ src, void* __restrict__ dst, 
 
 using namespace hds;
 
+static int norm_impl(const void* x, int64_t ld_in, void* delta, int delta_is_f32, int zero_delta, void* res_out,
+                     void* out, int64_t ld_out, const void* gamma, const void* beta, const int32_t* row_idx, int rows,
+                     int cols, float eps, int layer_norm, int post_norm, int dtype, const DeltaPeers& peers, void* stream);
+
 extern "C" int hds_norm(const void* x, int64_t ld_in, void* delta, int delta_is_f32, int zero_delta, void* res_out,
                         void* out, int64_t ld_out, const void* gamma, const void* beta, const int32_t* row_idx,
                         int rows, int cols, float eps, int layer_norm, int post_norm, int dtype, void* stream) {
+    DeltaPeers none;
+    memset(&none, 0, sizeof(none));
+    return norm_impl(x, ld_in, delta, delta_is_f32, zero_delta, res_out, out, ld_out, gamma, beta, row_idx, rows, cols,
+                     eps, layer_norm, post_norm, dtype, none, stream);
+}
+
+extern "C" int hds_norm_tp(const void* x, int64_t ld_in, const float* const* delta_peer_ptrs, int n_peers,
+                           float* zero_buf, void* res_out, void* out, int64_t ld_out, const void* gamma,
+                           const void* beta, int rows, int cols, float eps, int layer_norm, int dtype, void* stream) {
+    HDS_REQUIRE(n_peers >= 1 && n_peers <= 8, "hds_norm_tp: 1..8 peer buffers");
+    DeltaPeers peers;
+    memset(&peers, 0, sizeof(peers));
+    for (int i = 0; i < n_peers; ++i) peers.src[i] = delta_peer_ptrs[i];
+    peers.n = n_peers;
+    peers.zero_buf = zero_buf;
+    return norm_impl(x, ld_in, const_cast<float*>(delta_peer_ptrs[0]), 1, 0, res_out, out, ld_out, gamma, beta, nullptr,
+                     rows, cols, eps, layer_norm, 0, dtype, peers, stream);
+}
+
+static int norm_impl(const void* x, int64_t ld_in, void* delta, int delta_is_f32, int zero_delta, void* res_out,
+                     void* out, int64_t ld_out, const void* gamma, const void* beta, const int32_t* row_idx, int rows,
+                     int cols, float eps, int layer_norm, int post_norm, int dtype, const DeltaPeers& peers, void* stream) {
     HDS_REQUIRE(rows >= 0 && cols > 0 && cols % 8 == 0, "hds_norm: cols must be a positive multiple of 8");
     HDS_REQUIRE(dtype == 0 || dtype == 1, "hds_norm: dtype must be 0 (bf16) or 1 (fp16)");
     HDS_REQUIRE(delta == nullptr || row_idx == nullptr, "hds_norm: delta and row gather are mutually exclusive");
@@ -379,7 +433,7 @@ extern "C" int hds_norm(const void* x, int64_t ld_in, void* delta, int delta_is_
     const bool f32 = delta != nullptr && delta_is_f32;
 #define HDS_NORM_DISPATCH(BF, LN, F32)                                                                            \
     return launch_norm_vpt<BF, LN, F32>(rows, cols, x, delta, res_out, out, gamma, beta, row_idx, eps, zero_delta, \
-                                        post_norm, ld_in, ld_out, s)
+                                        post_norm, ld_in, ld_out, peers, s)
     if (dtype == 0) {
         if (layer_norm) { if (f32) HDS_NORM_DISPATCH(true, true, true); else HDS_NORM_DISPATCH(true, true, false); }
         else            { if (f32) HDS_NORM_DISPATCH(true, false, true); else HDS_NORM_DISPATCH(true, false, false); }

@@ -221,6 +221,21 @@ def norm(x: torch.Tensor, gamma: torch.Tensor, out: torch.Tensor, *, beta: Optio
     return out
 
 
+def norm_tp(x: torch.Tensor, gamma: torch.Tensor, out: torch.Tensor, delta_peer_ptrs: Sequence[int], *,
+            zero_buf: Optional[torch.Tensor] = None, beta: Optional[torch.Tensor] = None,
+            res_out: Optional[torch.Tensor] = None, eps: float = 1e-5, layer_norm: bool = False) -> torch.Tensor:
+    """Norm whose pending delta is the sum of every TP rank's fp32 partial-sum buffer, read over NVLink."""
+    cols = x.shape[-1]
+    arr = (ctypes.c_void_p * len(delta_peer_ptrs))(*delta_peer_ptrs)
+    lib = native.cuda_lib()
+    rc = lib.hds_norm_tp(_p(x), x.stride(-2) if x.dim() > 1 else cols, arr, len(delta_peer_ptrs), _p(zero_buf), _p(res_out),
+                         _p(out), out.stride(-2) if out.dim() > 1 else cols, _p(gamma), _p(beta), x.numel() // cols, cols,
+                         eps, 1 if layer_norm else 0, _dt(x), _stream())
+    native.check(rc, "hds_norm_tp")
+    _count()
+    return out
+
+
 def rope_kv_append(qkv: torch.Tensor, q_out: torch.Tensor, kv_cache_layer: torch.Tensor, tok_pos: torch.Tensor,
                    tok_slot: torch.Tensor, inv_freq: Optional[torch.Tensor], n_q_heads: int, n_kv_heads: int,
                    head_dim: int, rotary_dim: int, block_size: int) -> None:

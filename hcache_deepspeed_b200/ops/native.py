@@ -41,6 +41,7 @@ def _declare_cuda(lib: ctypes.CDLL) -> None:
         "hds_qkv_rope_proj": [P, L, P, L, I, I, I, P, P, P, P, P, P, I, I, I, I, I, P],
         "hds_restore_kv_proj_peers": [P, I, I, L, P, L, I, I, I, P, P, P, P, P, I, I, I, I, P],
         "hds_norm": [P, L, P, I, I, P, P, L, P, P, P, I, I, F, I, I, I, P],
+        "hds_norm_tp": [P, L, P, I, P, P, P, L, P, P, I, I, F, I, I, P],
         "hds_rope_kv_append": [P, L, P, P, P, P, P, I, I, I, I, I, I, I, I, P],
         "hds_embed": [P, P, P, P, I, I, P, I, I, I, I, P],
         "hds_gather_rows": [P, P, P, I, I, P],

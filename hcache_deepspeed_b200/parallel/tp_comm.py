@@ -28,11 +28,20 @@ from ..utils.logging import logger
 
 
 class FusedTPComm(TPComm):
+    """``mode``:
+
+    * ``"pull"`` (default) — every rank accumulates its partial sums locally (split-K atomics stay on-device) and
+      the consuming norm kernel adds up all ranks' buffers with plain loads over NVLink. Measured on 2xB200: remote
+      fp32 atomics made a 64-token forward ~2x slower than plain peer loads.
+    * ``"push"`` — the GEMM epilogue reduces its tile into every rank's buffer (``multimem.red`` on an NVLS multicast
+      address when the switch provides one, else ``red.sys`` to each peer mapping): GEMM -> all-reduce in one kernel.
+    """
     fused = True
 
-    def __init__(self, group, size: int, rank: int, device: torch.device) -> None:
+    def __init__(self, group, size: int, rank: int, device: torch.device, mode: str = "pull") -> None:
         super().__init__(group, size, rank)
         self.device = device
+        self.mode = mode
         self._symm = None
         self._bufs: List[torch.Tensor] = []
         self._handles = []
@@ -82,6 +91,16 @@ class FusedTPComm(TPComm):
                 return [int(p) + (base - b0) + byte_offset for p in hdl.buffer_ptrs]
         raise ValueError("tensor is not a symmetric allocation of this communicator")
 
+    def peer_view(self, t: torch.Tensor, peer: int) -> torch.Tensor:
+        """Tensor aliasing ``t``'s storage in rank ``peer``'s copy of the symmetric allocation (same shape)."""
+        base = t.data_ptr()
+        for buf, hdl in zip(self._bufs, self._handles):
+            b0 = buf.data_ptr()
+            if b0 <= base < b0 + buf.numel() * buf.element_size():
+                off = (base - b0) // buf.element_size()
+                return hdl.get_buffer(peer, tuple(t.shape), t.dtype, off)
+        raise ValueError("tensor is not a symmetric allocation of this communicator")
+
     def barrier(self) -> None:
         """Device-side barrier of the TP group on the current stream (flags in symmetric memory)."""
         self._handles[0].barrier(channel=1)
@@ -115,10 +134,11 @@ class FusedTPComm(TPComm):
         hdl.barrier(channel=0)
 
 
-def make_tp_comm(group, size: int, rank: int, device: torch.device) -> TPComm:
+def make_tp_comm(group, size: int, rank: int, device: torch.device, mode: str = "pull") -> TPComm:
     """Fused communicator when symmetric memory works on this system, else the NCCL baseline."""
     try:
-        return FusedTPComm(group, size, rank, device)
+        import os
+        return FusedTPComm(group, size, rank, device, mode=os.environ.get("HDS_TP_REDUCE", mode))
     except Exception as e:  # no symmetric memory support (driver / topology): keep serving over NCCL
         logger.warning(f"fused tensor-parallel collectives unavailable ({type(e).__name__}: {e}); using NCCL all-reduce")
         return TPComm(group=group, size=size, rank=rank)

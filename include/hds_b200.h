@@ -88,6 +88,16 @@ int hds_norm(const void* x, int64_t ld_in, void* delta, int delta_is_f32, int ze
              int64_t ld_out, const void* gamma, const void* beta, const int32_t* row_idx, int rows, int cols,
              float eps, int layer_norm, int post_norm, int dtype, void* stream);
 
+/* Tensor-parallel variant: the pending delta is the SUM over ranks of an fp32 buffer that each rank accumulated
+ * locally (hds_gemm_accum, red_mode 0) in symmetric memory. delta_peer_ptrs (HOST array) holds this rank's mappings
+ * of that buffer on all n_peers ranks; the kernel adds them up with loads over NVLink (pull all-reduce fused into the
+ * norm). zero_buf (optional) is a local rows x cols fp32 buffer to clear — the other half of the alternating pair.
+ * The caller places a device barrier between the GEMMs and this kernel.
+ * Ref: the dist.all_reduce + pre-norm pair of model_implementations/llama_v2/model.py:159-171. */
+int hds_norm_tp(const void* x, int64_t ld_in, const float* const* delta_peer_ptrs, int n_peers, float* zero_buf,
+                void* res_out, void* out, int64_t ld_out, const void* gamma, const void* beta, int rows, int cols,
+                float eps, int layer_norm, int dtype, void* stream);
+
 /* ---- ragged helpers ------------------------------------------------------------------------ */
 
 /* Unfused RoPE (rotate-half over the first rotary_dim dims) + paged KV append from a dense qkv[T, (nq+2nkv)*d].
