@@ -260,13 +260,18 @@ class InferenceEngineV2:
             graph = torch.cuda.CUDAGraph()
             side = torch.cuda.Stream(device=model.device)
             side.wait_stream(torch.cuda.current_stream())
+            from ...ops import kernels as _k
+            before = _k.launch_count
             with torch.cuda.stream(side):
                 with torch.cuda.graph(graph, stream=side):
                     static_logits = model.forward(batch, capture=False)[0]
             torch.cuda.current_stream().wait_stream(side)
-            entry = (graph, static_logits)
+            entry = (graph, static_logits, _k.launch_count - before)
+            _k.launch_count = before  # capture launched nothing; replays account for the kernels they run
             self._decode_graphs[key] = entry
         entry[0].replay()
+        from ...ops import kernels as _k
+        _k.launch_count += entry[2]
         self.graph_replays += 1
         return entry[1]
 

@@ -194,6 +194,7 @@ class RaggedTransformer:
             self.io_stream = torch.cuda.Stream(device=dev)
             self.restore_stage = buf(RESTORE_SLOTS, T, H)
             self.restore_stage_sym = None
+            self._slot_peer_ptrs = {}
             if self.tp_size > 1 and getattr(self.comm, "fused", False):
                 # per-rank slice of the staging ring in symmetric memory: peers' restore kernels read it over NVLink
                 # "copy" gather: full-size slots, each rank fills its own rows and pulls the peers' rows (one P2P read of
@@ -515,12 +516,9 @@ class RaggedTransformer:
             if self.tp_gather == "copy":
                 # pull every peer's rows once over NVLink into my full-size slot, then project locally
                 slot_t = self.restore_stage_sym[k]
-                for p in range(self.tp_size):
-                    if p == self.tp_rank:
-                        continue
-                    lo_p, hi_p, _ = shard_rows(T, self.tp_size, p)
-                    if hi_p > lo_p:
-                        slot_t[lo_p:hi_p].copy_(self.comm.peer_view(slot_t[lo_p:hi_p], p), non_blocking=True)
+                if k not in self._slot_peer_ptrs:
+                    self._slot_peer_ptrs[k] = self.comm.peer_ptrs_raw(slot_t)
+                self.ops.k.p2p_gather_rows(slot_t, self._slot_peer_ptrs[k], per, T, self.tp_rank)
                 self.comm.barrier()  # peers have read my rows: the slot may be refilled once my kernel is done
                 self.ops.restore_kv_proj(slot_t[:T], wk, bk, kv.get_cache(li), self.restore_pos[:T], self.restore_slot[:T],
                                          self.inv_freq, self.n_kv, self.d, s.rot_dim, kv.kv_block_size,

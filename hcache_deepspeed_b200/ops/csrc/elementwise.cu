@@ -373,6 +373,24 @@ __global__ void kv_blocks_copy_kernel(char* __restrict__ cache, char* __restrict
     }
 }
 
+// ---------------------------------------------------------------------------------------------
+// P2P row gather for the tensor-parallel restore: dst[r] = peer_of(r)[r] for every row not owned by this rank.
+// One launch pulls all peers' slices over NVLink (16-byte loads from peer-mapped symmetric memory).
+// ---------------------------------------------------------------------------------------------
+struct PeerPtrs {
+    const char* p[8];
+};
+__global__ void p2p_gather_rows_kernel(char* __restrict__ dst, const PeerPtrs peers, int rows_per_peer, int n_rows,
+                                       int64_t row_bytes, int my_rank) {
+    const int r = blockIdx.x;
+    const int owner = r / rows_per_peer;
+    if (r >= n_rows || owner == my_rank) return;
+    const uint4* src = reinterpret_cast<const uint4*>(peers.p[owner] + static_cast<int64_t>(r) * row_bytes);
+    uint4* d = reinterpret_cast<uint4*>(dst + static_cast<int64_t>(r) * row_bytes);
+    const int nvec = static_cast<int>(row_bytes >> 4);
+    for (int i = threadIdx.x; i < nvec; i += blockDim.x) d[i] = src[i];
+}
+
 // fp32 -> 16-bit convert (used to materialise accumulated fp32 partial sums), optional zeroing
 template <bool kBf16>
 __global__ void cvt_f32_kernel(float* __restrict__ src, void* __restrict__ dst, int64_t n, int zero_src) {
@@ -510,6 +528,20 @@ extern "C" int hds_kv_blocks_copy(void* cache, void* staging, const int32_t* blo
     kv_blocks_copy_kernel<<<grid, 256, 0, static_cast<cudaStream_t>(stream)>>>(
         reinterpret_cast<char*>(cache), reinterpret_cast<char*>(staging), block_ids, block_bytes, layer_stride_bytes,
         n_layers, to_staging);
+    HDS_CHECK_CUDA(cudaGetLastError());
+    return HDS_OK;
+}
+
+extern "C" int hds_p2p_gather_rows(void* dst, const void* const* peer_ptrs, int n_peers, int rows_per_peer, int n_rows,
+                                   int64_t row_bytes, int my_rank, void* stream) {
+    HDS_REQUIRE(n_peers >= 1 && n_peers <= 8, "hds_p2p_gather_rows: 1..8 peers");
+    HDS_REQUIRE(row_bytes % 16 == 0 && rows_per_peer > 0, "hds_p2p_gather_rows: rows must be 16-byte multiples");
+    if (n_rows == 0) return HDS_OK;
+    PeerPtrs pp;
+    memset(&pp, 0, sizeof(pp));
+    for (int i = 0; i < n_peers; ++i) pp.p[i] = reinterpret_cast<const char*>(peer_ptrs[i]);
+    p2p_gather_rows_kernel<<<n_rows, 256, 0, static_cast<cudaStream_t>(stream)>>>(reinterpret_cast<char*>(dst), pp,
+                                                                                  rows_per_peer, n_rows, row_bytes, my_rank);
     HDS_CHECK_CUDA(cudaGetLastError());
     return HDS_OK;
 }

@@ -293,6 +293,16 @@ def kv_blocks_copy(cache: torch.Tensor, staging: torch.Tensor, block_ids: torch.
     _count()
 
 
+def p2p_gather_rows(dst: torch.Tensor, peer_ptrs: Sequence[int], rows_per_peer: int, n_rows: int, my_rank: int) -> None:
+    """Fill ``dst[:n_rows]`` rows owned by other TP ranks from their symmetric buffers (one launch, NVLink loads)."""
+    arr = (ctypes.c_void_p * len(peer_ptrs))(*peer_ptrs)
+    lib = native.cuda_lib()
+    rc = lib.hds_p2p_gather_rows(_p(dst), arr, len(peer_ptrs), rows_per_peer, n_rows, dst.shape[-1] * dst.element_size(),
+                                 my_rank, _stream())
+    native.check(rc, "hds_p2p_gather_rows")
+    _count()
+
+
 def cvt_f32(src: torch.Tensor, dst: torch.Tensor, zero_src: bool = False) -> torch.Tensor:
     lib = native.cuda_lib()
     rc = lib.hds_cvt_f32(_p(src), _p(dst), src.numel(), 1 if zero_src else 0, _dt(dst), _stream())

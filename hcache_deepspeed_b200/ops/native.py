@@ -48,6 +48,7 @@ def _declare_cuda(lib: ctypes.CDLL) -> None:
         "hds_argmax": [P, L, I, I, P, P, I, P],
         "hds_kv_blocks_copy": [P, P, P, I, I, L, L, I, P],
         "hds_cvt_f32": [P, P, L, I, I, P],
+        "hds_p2p_gather_rows": [P, P, I, I, I, L, I, P],
         "hds_paged_attention_splitkv": [P, P, P, L, P, I, P, I, I, I, I, I, I, I, F, P, L, I, P],
         "hds_paged_attention_prefill": [P, P, P, L, P, I, P, I, I, I, I, I, I, F, I, P, L, I, P],
     }

@@ -123,6 +123,12 @@ int hds_argmax(const void* logits, int64_t ld, int n_rows, int V, int32_t* out_i
 int hds_kv_blocks_copy(void* cache, void* staging, const int32_t* block_ids, int n_sel, int n_layers,
                        int64_t block_bytes, int64_t layer_stride_bytes, int to_staging, void* stream);
 
+/* Row gather across tensor-parallel peers: rows [p*rows_per_peer, (p+1)*rows_per_peer) of `dst` are copied from the
+ * same rows of peer p's buffer (peer_ptrs[p]: HOST array of this rank's mappings), except this rank's own rows.
+ * No reference counterpart (the reference has no TP restore). */
+int hds_p2p_gather_rows(void* dst, const void* const* peer_ptrs, int n_peers, int rows_per_peer, int n_rows,
+                        int64_t row_bytes, int my_rank, void* stream);
+
 /* dst (16-bit) = src (fp32); optionally zero src. */
 int hds_cvt_f32(float* src, void* dst, int64_t n, int zero_src, int dtype, void* stream);
 
