@@ -74,6 +74,7 @@ paged_attn_prefill_kernel(const __grid_constant__ CUtensorMap tmap_q, const __gr
     uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(o_full + 1);
 
     const uint32_t warp = warp_id(), lane = lane_id();
+    pdl_enter();  // PDL: the next kernel may be scheduled; this one needs its predecessor's Q and KV writes
     const hds_attn_item item = a.items[blockIdx.x];
     const int head = blockIdx.y;
     const int kvh = head / (a.n_q_heads / a.n_kv_heads);
@@ -385,8 +386,7 @@ static int launch_prefill(const CUtensorMap& tq, const CUtensorMap& tkv, const P
         configured[dev & 63] = true;
     }
     dim3 grid(n_items, a.n_q_heads, a.n_splits);
-    kern<<<grid, kPfThreads, pf_smem_bytes<D>(), s>>>(tq, tkv, a);
-    HDS_CHECK_CUDA(cudaGetLastError());
+    HDS_CHECK_CUDA(launch_kernel(kern, grid, dim3(kPfThreads), pf_smem_bytes<D>(), s, tq, tkv, a));
     return HDS_OK;
 }
 

@@ -65,6 +65,7 @@ paged_attn_splitkv_kernel(const __grid_constant__ CUtensorMap tmap_kv, const Att
     constexpr int CH = D / 16;                     // 16-byte K chunks per lane (two lanes share a token)
     constexpr int EPL = D / 32;                    // output dims per lane in the PV step
 
+    pdl_enter();  // PDL: the next kernel may be scheduled; this one needs its predecessor's Q and KV writes
     extern __shared__ uint8_t smem_raw[];
     uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
     uint8_t* stages = smem;
@@ -338,8 +339,7 @@ static int launch_splitkv(const CUtensorMap& tm, const AttnArgs& a, int n_items,
         configured[dev & 63] = true;
     }
     dim3 grid(n_items, a.n_kv_heads, a.n_splits);
-    kern<<<grid, kAttnThreads, attn_smem_bytes<D, R>(), s>>>(tm, a);
-    HDS_CHECK_CUDA(cudaGetLastError());
+    HDS_CHECK_CUDA(launch_kernel(kern, grid, dim3(kAttnThreads), attn_smem_bytes<D, R>(), s, tm, a));
     return HDS_OK;
 }
 

@@ -47,6 +47,7 @@ norm_kernel(const void* __restrict__ x_in, void* delta, void* res_out, void* __r
             const void* __restrict__ gamma, const void* __restrict__ beta, const int32_t* __restrict__ row_idx,
             int cols, float eps, int zero_delta, int post_norm, int64_t ld_in, int64_t ld_out, const DeltaPeers peers) {
     __shared__ float red[kNormThreads / 32];
+    pdl_enter();
     const int r_out = blockIdx.x;
     const int r_in = row_idx ? row_idx[r_out] : r_out;
     const int nvec = cols >> 3;
@@ -186,9 +187,8 @@ static int launch_norm_vpt(int rows, int cols, const void* x, void* delta, void*
     const int nvec = cols / 8;
     const int vpt = (nvec + kNormThreads - 1) / kNormThreads;
 #define HDS_NORM_LAUNCH(V)                                                                                        \
-    norm_kernel<V, kBf16, kLayerNorm, kDeltaF32><<<rows, kNormThreads, 0, s>>>(x, delta, res_out, out, gamma, beta, \
-                                                                               row_idx, cols, eps, zero_delta,      \
-                                                                               post_norm, ld_in, ld_out, peers)
+    launch_kernel(norm_kernel<V, kBf16, kLayerNorm, kDeltaF32>, dim3(rows), dim3(kNormThreads), 0, s, x, delta,    \
+                  res_out, out, gamma, beta, row_idx, cols, eps, zero_delta, post_norm, ld_in, ld_out, peers)
     if (vpt <= 1) HDS_NORM_LAUNCH(1);
     else if (vpt <= 2) HDS_NORM_LAUNCH(2);
     else if (vpt <= 4) HDS_NORM_LAUNCH(4);
@@ -211,6 +211,7 @@ __global__ void rope_kv_append_kernel(const void* __restrict__ qkv, int64_t ld_q
                                       void* __restrict__ kv_cache, const int32_t* __restrict__ tok_pos,
                                       const int32_t* __restrict__ tok_slot, const float* __restrict__ inv_freq,
                                       int n_q, int n_kv, int d, int rotary_dim, int block_size, int do_rope) {
+    pdl_enter();
     const int t = blockIdx.x;
     const int head = blockIdx.y;
     const int vi = threadIdx.x;
@@ -261,6 +262,7 @@ template <bool kBf16>
 __global__ void embed_kernel(const int32_t* __restrict__ ids, const void* __restrict__ W, const void* __restrict__ P,
                              const int32_t* __restrict__ tok_pos, int pos_offset, int max_pos, void* __restrict__ out,
                              int H, int vocab) {
+    pdl_enter();
     const int t = blockIdx.x;
     const int id = ids[t];
     const int nvec = H >> 3;
@@ -288,6 +290,7 @@ __global__ void embed_kernel(const int32_t* __restrict__ ids, const void* __rest
 // rows gather: out[i] = x[row_idx[i]]
 __global__ void gather_rows_kernel(const void* __restrict__ x, const int32_t* __restrict__ row_idx,
                                    void* __restrict__ out, int H) {
+    pdl_enter();
     const int i = blockIdx.x;
     const int r = row_idx[i];
     const int nvec = H >> 3;
@@ -306,6 +309,7 @@ argmax_kernel(const void* __restrict__ logits, int64_t ld, int V, int32_t* __res
               float* __restrict__ out_vals) {
     __shared__ float sv[32];
     __shared__ int si[32];
+    pdl_enter();
     const int s = blockIdx.x;
     float best = -INFINITY;
     int bi = 0x7fffffff;
@@ -394,6 +398,7 @@ __global__ void p2p_gather_rows_kernel(char* __restrict__ dst, const PeerPtrs pe
 // fp32 -> 16-bit convert (used to materialise accumulated fp32 partial sums), optional zeroing
 template <bool kBf16>
 __global__ void cvt_f32_kernel(float* __restrict__ src, void* __restrict__ dst, int64_t n, int zero_src) {
+    pdl_enter();
     const int64_t i = (static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x) * 4;
     if (i + 3 < n) {
         float4 v = *reinterpret_cast<float4*>(src + i);
@@ -475,11 +480,11 @@ extern "C" int hds_rope_kv_append(const void* qkv, int64_t ld_qkv, void* q_out, 
     const int threads = ((head_dim / 8 + 31) / 32) * 32;
     cudaStream_t s = static_cast<cudaStream_t>(stream);
     if (dtype == 0)
-        rope_kv_append_kernel<true><<<grid, threads, 0, s>>>(qkv, ld_qkv, q_out, kv_cache_layer, tok_pos, tok_slot,
+        launch_kernel(rope_kv_append_kernel<true>, grid, dim3(threads), 0, s, qkv, ld_qkv, q_out, kv_cache_layer, tok_pos, tok_slot,
                                                              inv_freq, n_q_heads, n_kv_heads, head_dim, rotary_dim,
                                                              block_size, do_rope);
     else
-        rope_kv_append_kernel<false><<<grid, threads, 0, s>>>(qkv, ld_qkv, q_out, kv_cache_layer, tok_pos, tok_slot,
+        launch_kernel(rope_kv_append_kernel<false>, grid, dim3(threads), 0, s, qkv, ld_qkv, q_out, kv_cache_layer, tok_pos, tok_slot,
                                                               inv_freq, n_q_heads, n_kv_heads, head_dim, rotary_dim,
                                                               block_size, do_rope);
     HDS_CHECK_CUDA(cudaGetLastError());
@@ -493,9 +498,9 @@ extern "C" int hds_embed(const int32_t* ids, const void* W, const void* P, const
     cudaStream_t s = static_cast<cudaStream_t>(stream);
     const int threads = H / 8 >= 256 ? 256 : 128;
     if (dtype == 0)
-        embed_kernel<true><<<T, threads, 0, s>>>(ids, W, P, tok_pos, pos_offset, max_pos, out, H, vocab);
+        launch_kernel(embed_kernel<true>, dim3(T), dim3(threads), 0, s, ids, W, P, tok_pos, pos_offset, max_pos, out, H, vocab);
     else
-        embed_kernel<false><<<T, threads, 0, s>>>(ids, W, P, tok_pos, pos_offset, max_pos, out, H, vocab);
+        launch_kernel(embed_kernel<false>, dim3(T), dim3(threads), 0, s, ids, W, P, tok_pos, pos_offset, max_pos, out, H, vocab);
     HDS_CHECK_CUDA(cudaGetLastError());
     return HDS_OK;
 }
@@ -503,7 +508,7 @@ extern "C" int hds_embed(const int32_t* ids, const void* W, const void* P, const
 extern "C" int hds_gather_rows(const void* x, const int32_t* row_idx, void* out, int n_rows, int H, void* stream) {
     HDS_REQUIRE(H % 8 == 0, "hds_gather_rows: hidden size must be a multiple of 8");
     if (n_rows == 0) return HDS_OK;
-    gather_rows_kernel<<<n_rows, 256, 0, static_cast<cudaStream_t>(stream)>>>(x, row_idx, out, H);
+    launch_kernel(gather_rows_kernel, dim3(n_rows), dim3(256), 0, static_cast<cudaStream_t>(stream), x, row_idx, out, H);
     HDS_CHECK_CUDA(cudaGetLastError());
     return HDS_OK;
 }
@@ -513,9 +518,9 @@ extern "C" int hds_argmax(const void* logits, int64_t ld, int n_rows, int V, int
     HDS_REQUIRE(dtype >= 0 && dtype <= 2, "hds_argmax: dtype 0 (bf16) / 1 (fp16) / 2 (fp32)");
     if (n_rows == 0) return HDS_OK;
     cudaStream_t s = static_cast<cudaStream_t>(stream);
-    if (dtype == 0) argmax_kernel<0><<<n_rows, 1024, 0, s>>>(logits, ld, V, out_ids, out_vals);
-    else if (dtype == 1) argmax_kernel<1><<<n_rows, 1024, 0, s>>>(logits, ld, V, out_ids, out_vals);
-    else argmax_kernel<2><<<n_rows, 1024, 0, s>>>(logits, ld, V, out_ids, out_vals);
+    if (dtype == 0) launch_kernel(argmax_kernel<0>, dim3(n_rows), dim3(1024), 0, s, logits, ld, V, out_ids, out_vals);
+    else if (dtype == 1) launch_kernel(argmax_kernel<1>, dim3(n_rows), dim3(1024), 0, s, logits, ld, V, out_ids, out_vals);
+    else launch_kernel(argmax_kernel<2>, dim3(n_rows), dim3(1024), 0, s, logits, ld, V, out_ids, out_vals);
     HDS_CHECK_CUDA(cudaGetLastError());
     return HDS_OK;
 }
@@ -551,8 +556,8 @@ extern "C" int hds_cvt_f32(float* src, void* dst, int64_t n, int zero_src, int d
     const int threads = 256;
     const int64_t blocks = ((n + 3) / 4 + threads - 1) / threads;
     cudaStream_t s = static_cast<cudaStream_t>(stream);
-    if (dtype == 0) cvt_f32_kernel<true><<<static_cast<unsigned>(blocks), threads, 0, s>>>(src, dst, n, zero_src);
-    else cvt_f32_kernel<false><<<static_cast<unsigned>(blocks), threads, 0, s>>>(src, dst, n, zero_src);
+    if (dtype == 0) launch_kernel(cvt_f32_kernel<true>, dim3(static_cast<unsigned>(blocks)), dim3(threads), 0, s, src, dst, n, zero_src);
+    else launch_kernel(cvt_f32_kernel<false>, dim3(static_cast<unsigned>(blocks)), dim3(threads), 0, s, src, dst, n, zero_src);
     HDS_CHECK_CUDA(cudaGetLastError());
     return HDS_OK;
 }

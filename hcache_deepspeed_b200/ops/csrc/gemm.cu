@@ -1,6 +1,7 @@
 // Launchers for the tcgen05 GEMM family (see gemm_core.cuh for the kernel).
 #include <stdlib.h>
 #include "gemm_core.cuh"
+#include "gemm_skinny.cuh"
 #include "hds_host.cuh"
 #include "../../../include/hds_b200.h"
 
@@ -22,8 +23,8 @@ static int launch_gemm_inst(const CUtensorMap& ta, const CUtensorMap& tw, const 
                                             static_cast<int>(gemm_smem_bytes(BN, AM))));
         configured[dev & 63] = true;
     }
-    kern<<<grid, kGemmThreads, gemm_smem_bytes(BN, AM), stream>>>(ta, tw, args, g_peer_maps ? *g_peer_maps : kNoPeers);
-    HDS_CHECK_CUDA(cudaGetLastError());
+    HDS_CHECK_CUDA(launch_kernel(kern, dim3(grid), dim3(kGemmThreads), gemm_smem_bytes(BN, AM), stream, ta, tw, args,
+                                 g_peer_maps ? *g_peer_maps : kNoPeers));
     return HDS_OK;
 }
 
@@ -116,6 +117,93 @@ struct Operands {
     CUtensorMap ta, tw;
 };
 
+// ---- decode-size M: feature-major weight-streaming kernel (gemm_skinny.cuh) -------------------------------
+static inline int skinny_nt(int M) { return M <= 16 ? 16 : M <= 32 ? 32 : 64; }
+static bool skinny_enabled() {
+    static const int on = getenv("HDS_GEMM_SKINNY") ? atoi(getenv("HDS_GEMM_SKINNY")) : 1;
+    return on != 0;
+}
+
+template <int NT, int EPI, bool kBf16>
+static int launch_skinny_inst(const CUtensorMap& tw, const CUtensorMap& tx, const SkinnyArgs& a, int grid,
+                              cudaStream_t stream) {
+    auto kern = gemm_skinny_kernel<NT, EPI, kBf16>;
+    static bool configured[64] = {false};
+    int dev = 0;
+    cudaGetDevice(&dev);
+    if (!configured[dev & 63]) {
+        HDS_CHECK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                            static_cast<int>(skinny_smem_bytes(NT))));
+        configured[dev & 63] = true;
+    }
+    HDS_CHECK_CUDA(launch_kernel(kern, dim3(grid), dim3(kGemmThreads), skinny_smem_bytes(NT), stream, tw, tx, a));
+    return HDS_OK;
+}
+
+template <int EPI, bool kBf16>
+static int launch_skinny_nt(int nt, const CUtensorMap& tw, const CUtensorMap& tx, const SkinnyArgs& a, int grid,
+                            cudaStream_t stream) {
+    if (nt == 16) return launch_skinny_inst<16, EPI, kBf16>(tw, tx, a, grid, stream);
+    if (nt == 32) return launch_skinny_inst<32, EPI, kBf16>(tw, tx, a, grid, stream);
+    return launch_skinny_inst<64, EPI, kBf16>(tw, tx, a, grid, stream);
+}
+
+// One CTA per (128-feature tile, K split); splits fill the resident slots (SMs x CTAs per SM) once.
+static int launch_skinny(int epi, bool bf16, const void* X, int64_t ldx, const void* W, int64_t ldw, int M, int N,
+                         int K, int act, const void* bias, void* out, int64_t ldo, float* accum, int64_t ld_accum,
+                         void* ws, int64_t ws_bytes, int want_splits, cudaStream_t stream) {
+    HDS_REQUIRE(M > 0 && N > 0 && K > 0, "gemm: empty problem");
+    HDS_REQUIRE(K % 8 == 0 && ldx % 8 == 0 && ldw % 8 == 0, "gemm: K, lda, ldw must be multiples of 8 elements");
+    const int nt = skinny_nt(M);
+    const int n_tiles = (N + kSkinnyBF - 1) / kSkinnyBF;
+    const int kb_total = (K + kGemmBK - 1) / kGemmBK;
+    const int64_t ws_data = (static_cast<int64_t>(n_tiles) * kSkinnyBF * nt * 4 + 255) & ~int64_t(255);
+    const bool can_split = epi == EPI_RED_F32 || (ws != nullptr && ws_bytes >= ws_data + static_cast<int64_t>(n_tiles) * 16);
+    int splits = 1;
+    if (can_split) {
+        if (want_splits > 0) {
+            splits = want_splits;
+        } else {
+            const int slots = sm_count() * skinny_occupancy(nt);
+            splits = slots / n_tiles;
+            if (splits > kb_total / 4) splits = kb_total / 4;
+            if (splits > 8) splits = 8;
+        }
+        if (splits < 1) splits = 1;
+        if (splits > kb_total) splits = kb_total;
+    }
+    const int per = (kb_total + splits - 1) / splits;
+    splits = (kb_total + per - 1) / per;
+    SkinnyArgs a;
+    memset(&a, 0, sizeof(a));
+    a.M = M; a.N = N; a.K = K;
+    a.splits = splits;
+    a.kb_per_split = per;
+    a.act = act;
+    a.out = out; a.ldo = ldo; a.bias = bias;
+    a.accum = accum; a.ld_accum = ld_accum;
+    if (splits > 1 && epi != EPI_RED_F32) {
+        a.ws = reinterpret_cast<float*>(ws);
+        a.tickets = reinterpret_cast<int32_t*>(reinterpret_cast<char*>(ws) + ws_data);
+    }
+    CUtensorMap tw, tx;
+    int rc = make_tmap_2d_16b(&tw, W, static_cast<uint64_t>(K), static_cast<uint64_t>(N),
+                              static_cast<uint64_t>(ldw) * 2, kGemmBK, kSkinnyBF, bf16);
+    if (rc) return rc;
+    rc = make_tmap_2d_16b(&tx, X, static_cast<uint64_t>(K), static_cast<uint64_t>(M), static_cast<uint64_t>(ldx) * 2,
+                          kGemmBK, nt, bf16);
+    if (rc) return rc;
+    const int grid = n_tiles * splits;
+    if (bf16) {
+        if (epi == EPI_STORE) return launch_skinny_nt<EPI_STORE, true>(nt, tw, tx, a, grid, stream);
+        if (epi == EPI_GATED) return launch_skinny_nt<EPI_GATED, true>(nt, tw, tx, a, grid, stream);
+        return launch_skinny_nt<EPI_RED_F32, true>(nt, tw, tx, a, grid, stream);
+    }
+    if (epi == EPI_STORE) return launch_skinny_nt<EPI_STORE, false>(nt, tw, tx, a, grid, stream);
+    if (epi == EPI_GATED) return launch_skinny_nt<EPI_GATED, false>(nt, tw, tx, a, grid, stream);
+    return launch_skinny_nt<EPI_RED_F32, false>(nt, tw, tx, a, grid, stream);
+}
+
 static int prepare(GemmArgs& g, Operands& ops, const void* A, int64_t lda, const void* W, int64_t ldw, int M, int N,
                    int K, bool bf16, int bn, int splits) {
     HDS_REQUIRE(M > 0 && N > 0 && K > 0, "gemm: empty problem");
@@ -174,7 +262,10 @@ static inline int64_t align256(int64_t x) { return (x + 255) & ~int64_t(255); }
 
 extern "C" int64_t hds_gemm_splitk_workspace_bytes(int M, int N) {
     // fp32 partial sums [M, N] + tickets for up to N/32 tiles x 4 quadrants
-    return align256(static_cast<int64_t>(M) * N * 4) + align256((static_cast<int64_t>(N) / 32 + 1) * 4 * 4);
+    // (the feature-major kernel for M <= 64 pads rows to its token tile and N to 128)
+    const int64_t rows = M <= 64 ? skinny_nt(M) : M;
+    const int64_t cols = (static_cast<int64_t>(N) + 127) / 128 * 128;
+    return align256(rows * cols * 4) + align256((static_cast<int64_t>(N) / 32 + 1) * 4 * 4);
 }
 
 extern "C" int hds_gemm(const void* A, int64_t lda, const void* W, int64_t ldw, int M, int N, int K, int dtype,
@@ -183,6 +274,11 @@ extern "C" int hds_gemm(const void* A, int64_t lda, const void* W, int64_t ldw, 
     HDS_REQUIRE(epilogue == EPI_STORE || epilogue == EPI_GATED, "hds_gemm: epilogue must be 0 (store) or 1 (gated)");
     HDS_REQUIRE(dtype == 0 || dtype == 1, "hds_gemm: dtype must be 0 (bf16) or 1 (fp16)");
     HDS_REQUIRE(epilogue != EPI_GATED || (N % 2 == 0), "hds_gemm: gated epilogue needs an even N");
+    // measured (profiles/kernel_bench.jsonl): the feature-major kernel wins for M <= 16 everywhere and for the gated
+    // MLP-1 up to 64 tokens (1.3-1.5x); plain stores at 32-64 tokens stay on the token-major kernel
+    if (M <= 64 && ldw >= 0 && (bn == -1 || (bn == 0 && skinny_enabled() && (M <= 16 || epilogue == EPI_GATED))))
+        return launch_skinny(epilogue, dtype == 0, A, lda, W, ldw, M, N, K, act, bias, out, ldo, nullptr, 0, splitk_ws,
+                             splitk_ws_bytes, splits, static_cast<cudaStream_t>(stream));
     GemmArgs g;
     memset(&g, 0, sizeof(g));
     Operands ops;
@@ -221,6 +317,9 @@ extern "C" int hds_gemm_accum(const void* A, int64_t lda, const void* W, int64_t
     HDS_REQUIRE(dtype == 0 || dtype == 1, "hds_gemm_accum: dtype must be 0 (bf16) or 1 (fp16)");
     HDS_REQUIRE(n_targets >= 1 && n_targets <= kMaxPeers, "hds_gemm_accum: 1..8 accumulation targets");
     HDS_REQUIRE(red_mode >= 0 && red_mode <= 2, "hds_gemm_accum: red_mode 0 (local) / 1 (p2p) / 2 (multicast)");
+    if (M <= 64 && ldw >= 0 && red_mode == 0 && n_targets == 1 && (bn == -1 || (bn == 0 && skinny_enabled() && M <= 16)))
+        return launch_skinny(EPI_RED_F32, dtype == 0, A, lda, W, ldw, M, N, K, 0, bias, nullptr, 0, accum_ptrs[0],
+                             ld_accum, nullptr, 0, splits, static_cast<cudaStream_t>(stream));
     GemmArgs g;
     memset(&g, 0, sizeof(g));
     Operands ops;

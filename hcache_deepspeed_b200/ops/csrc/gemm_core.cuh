@@ -412,6 +412,10 @@ gemm_tn_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
     tc_fence_after();
     const uint32_t tmem_base = *tmem_slot;
 
+    // PDL: the set-up above overlapped the previous kernel's tail; from here on its results are needed
+    griddep_launch_dependents();
+    griddep_wait();
+
     if (warp == 0) {
         // ===================== TMA producer =====================
         if (lane == 0) {

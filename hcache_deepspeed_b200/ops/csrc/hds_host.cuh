@@ -6,7 +6,9 @@
 #include <stdint.h>
 #include <stdio.h>
 #include <string.h>
+#include <stdlib.h>
 #include <mutex>
+#include <utility>
 
 namespace hds {
 
@@ -37,6 +39,29 @@ inline void set_error(const char* msg) {
             return ::hds::HDS_ERR_BAD_ARG;   \
         }                                    \
     } while (0)
+
+// Every kernel of the library is launched with the programmatic-stream-serialization attribute (PDL): it may begin
+// while its predecessor drains and synchronises with `griddepcontrol.wait` (hds_ptx.cuh). HDS_PDL=0 turns it off.
+inline bool pdl_enabled() {
+    static const int on = getenv("HDS_PDL") ? atoi(getenv("HDS_PDL")) : 1;
+    return on != 0;
+}
+template <typename... KArgs, typename... Args>
+inline cudaError_t launch_kernel(void (*kern)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t stream,
+                                 Args&&... args) {
+    cudaLaunchConfig_t cfg;
+    memset(&cfg, 0, sizeof(cfg));
+    cfg.gridDim = grid;
+    cfg.blockDim = block;
+    cfg.dynamicSmemBytes = smem;
+    cfg.stream = stream;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = pdl_enabled() ? 1 : 0;
+    cfg.attrs = attr;
+    cfg.numAttrs = 1;
+    return cudaLaunchKernelEx(&cfg, kern, std::forward<Args>(args)...);
+}
 
 inline int sm_count() {
     static int cached[64] = {0};

@@ -20,6 +20,17 @@ namespace hds {
 __device__ __forceinline__ uint32_t smem_u32(const void* p) {
     return static_cast<uint32_t>(__cvta_generic_to_shared(p));
 }
+// Programmatic dependent launch (PDL). Kernels launched through hds::launch_kernel may start while the previous
+// kernel of the stream is still draining: `griddep_launch_dependents` lets the NEXT kernel's CTAs be scheduled
+// once every CTA of this grid has issued it; `griddep_wait` blocks until all prerequisite grids have completed
+// and their writes are visible. Everything before the wait may only touch memory no kernel writes (weights).
+__device__ __forceinline__ void griddep_launch_dependents() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+__device__ __forceinline__ void griddep_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+__device__ __forceinline__ void pdl_enter() {
+    griddep_launch_dependents();
+    griddep_wait();
+}
+
 __device__ __forceinline__ uint32_t lane_id() { return threadIdx.x & 31; }
 __device__ __forceinline__ uint32_t warp_id() { return __shfl_sync(0xffffffffu, threadIdx.x >> 5, 0); }
 

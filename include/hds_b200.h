@@ -28,7 +28,8 @@ const char* hds_last_error(void);
 
 /* out = epilogue(A[M,K] * W[N,K]^T + bias).  epilogue 0: act();  1: gated — columns are interleaved
  * (gate, up) pairs, out has N/2 columns: out[:, j] = act(c[2j]) * c[2j+1].  act: 0 id, 1 gelu, 2 relu,
- * 3 silu, 4 gelu-tanh.  bn: tile width override (0 = heuristic).
+ * 3 silu, 4 gelu-tanh.  bn: tile width override (0 = heuristic; -1 = force the
+ * feature-major weight-streaming kernel of gemm_skinny.cuh, M <= 64 only).
  * Ref: core_ops/blas_kernels/blas.h:31-136 + bias_activations + gated_activations.
  * Split-K (decode-size M <= 128): pass a zero-initialised scratch buffer of at least
  * hds_gemm_splitk_workspace_bytes(M, N) bytes; partial sums meet there and the last split applies the

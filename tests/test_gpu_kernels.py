@@ -89,6 +89,32 @@ def test_gemm_bias_act(act):
     torch.testing.assert_close(out.float(), want, **tol(torch.bfloat16))
 
 
+@pytest.mark.parametrize("dtype", DTYPES)
+@pytest.mark.parametrize("M", [1, 16, 17, 33, 64])
+@pytest.mark.parametrize("mode", ["store", "gated", "accum"])
+@pytest.mark.parametrize("use_ws", [False, True])
+def test_gemm_skinny(dtype, M, mode, use_ws):
+    """Decode-size M takes the feature-major weight-streaming kernel (gemm_skinny.cuh): ragged N and K, every token
+    tile (16/32/64; bn=-1 forces the kernel for every M <= 64), with and without split-K scratch; scratch must come back zeroed."""
+    torch.manual_seed(M)
+    N, K_ = (690 if mode == "gated" else 1000), 2120
+    a, w, b = rand(M, K_, dtype=dtype), rand(N, K_, dtype=dtype, scale=K_ ** -0.5), rand(N, dtype=dtype)
+    ws = torch.zeros(K().gemm_splitk_workspace_bytes(M, N), dtype=torch.uint8, device="cuda") if use_ws else None
+    for rep in range(2):
+        if mode == "accum":
+            acc = torch.zeros(M, N, device="cuda", dtype=torch.float32)
+            K().gemm_accum(a, w, acc, bias=b, bn=-1)
+            want = ref.gemm(a, w, bias=b, out_dtype=torch.float32)
+            torch.testing.assert_close(acc, want, rtol=2e-3, atol=2e-3)
+        else:
+            gated = mode == "gated"
+            out = K().gemm(a, w, bias=b, act=3 if gated else 2, gated=gated, workspace=ws, bn=-1)
+            want = ref.gemm(a, w, bias=b, act=3 if gated else 2, gated=gated, out_dtype=torch.float32)
+            torch.testing.assert_close(out.float(), want, **tol(dtype))
+    if ws is not None:
+        assert int(ws.view(torch.int32).abs().max()) == 0
+
+
 @pytest.mark.parametrize("M", [5, 128, 700])
 def test_gemm_gated(M):
     torch.manual_seed(2)

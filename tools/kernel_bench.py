@@ -76,20 +76,20 @@ def bench_gemm():
 
 
 def bench_decode_gemm():
-    for M in (16, 64):
+    for M in (8, 32, 64):
         for (N, Kd, kind) in [(12288, 4096, "store"), (22016, 4096, "gated"), (4096, 4096, "accum"), (4096, 11008, "accum"),
                               (32000, 4096, "store")]:
             a, w = rand(M, Kd), rand(N, Kd, scale=Kd ** -0.5)
             wbytes = N * Kd * 2
             if kind == "accum":
                 acc = torch.zeros(M, N, device=dev, dtype=torch.float32)
-                for bn, splits in ((0, 0), (128, 4), (128, 9), (64, 2), (64, 4), (128, 1)):
+                for bn, splits in ((0, 0), (0, 1), (0, 2), (0, 4), (0, 8), (0, 13), (128, 4), (128, 9), (64, 4)):
                     med, mn = timeit(lambda: K.gemm_accum(a, w, acc, bn=bn, splits=splits))
                     report(f"decode_gemm_accum M{M} N{N} K{Kd} bn{bn} splits{splits}", med, mn, bytes_=wbytes)
             else:
                 out = torch.empty(M, N // 2 if kind == "gated" else N, device=dev, dtype=torch.bfloat16)
                 ws = torch.zeros(K.gemm_splitk_workspace_bytes(M, N), dtype=torch.uint8, device=dev)
-                for bn, splits in ((0, 0), (128, 1), (128, 2), (128, 3), (128, 5), (64, 2), (64, 4)):
+                for bn, splits in ((0, 0), (0, 1), (0, 2), (0, 4), (0, 8), (128, 1), (128, 3), (64, 2)):
                     med, mn = timeit(lambda: K.gemm(a, w, act=3 if kind == "gated" else 0, gated=kind == "gated", out=out,
                                                     bn=bn, splits=splits, workspace=ws))
                     report(f"decode_gemm_{kind} M{M} N{N} K{Kd} bn{bn} splits{splits}", med, mn, bytes_=wbytes)
