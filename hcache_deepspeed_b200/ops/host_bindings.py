@@ -2,7 +2,7 @@
 from __future__ import annotations
 
 import ctypes
-from ctypes import POINTER, Structure, c_char_p, c_int, c_int32, c_int64, c_void_p
+from ctypes import POINTER, Structure, c_char_p, c_float, c_int, c_int32, c_int64, c_void_p
 
 
 class SeqIn(Structure):
@@ -47,3 +47,11 @@ def declare(lib: ctypes.CDLL) -> None:
     lib.hds_mem_lock.restype = I
     lib.hds_mem_unlock.argtypes = [P, L]
     lib.hds_mem_unlock.restype = I
+
+    F = c_float
+    lib.hds_cpu_adam_step.argtypes = [P, P, P, P, L, F, F, F, F, F, I, I, I, P, I, I]
+    lib.hds_cpu_adam_step.restype = I
+    lib.hds_cpu_adagrad_step.argtypes = [P, P, P, L, F, F, F, P, I, I]
+    lib.hds_cpu_adagrad_step.restype = I
+    lib.hds_cpu_lion_step.argtypes = [P, P, P, L, F, F, F, F, P, I, I]
+    lib.hds_cpu_lion_step.restype = I

@@ -51,6 +51,8 @@ def _declare_cuda(lib: ctypes.CDLL) -> None:
         "hds_p2p_gather_rows": [P, P, I, I, I, L, I, P],
         "hds_paged_attention_splitkv": [P, P, P, L, P, I, P, I, I, I, I, I, I, I, F, P, L, I, P],
         "hds_paged_attention_prefill": [P, P, P, L, P, I, P, I, I, I, I, I, I, F, I, P, L, I, P],
+        "hds_multi_tensor_adam": [I, P, P, P, P, P, I, I, F, F, F, F, F, I, I, I, F, P],
+        "hds_multi_tensor_lion": [I, P, P, P, P, I, I, F, F, F, F, F, P],
     }
     for name, argtypes in sigs.items():
         fn = getattr(lib, name)

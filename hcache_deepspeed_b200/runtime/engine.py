@@ -1,0 +1,886 @@
+"""DeepSpeedEngine — the training engine returned by ``initialize()``.
+
+``loss = engine(batch); engine.backward(loss); engine.step()`` with gradient accumulation, mixed precision
+(fp16 + loss scaling, bf16 with fp32 masters), ZeRO stages 0-3 (+ CPU optimizer offload), gradient clipping,
+LR schedules, data loader construction, monitors / timers / FLOPS profiler, and checkpoint save / load.
+
+Behavioural reference: ``deepspeed/runtime/engine.py`` (DeepSpeedEngine :183; forward :2006, backward :2165,
+step :2352, _take_model_step :2279, allreduce_gradients :2088, save_checkpoint :3230, load_checkpoint :2850,
+_configure_optimizer :1370, _configure_zero_optimizer :1660) and ``deepspeed/__init__.py:69-235`` (initialize).
+Data-parallel gradient averaging without ZeRO is a bucketed flat all-reduce; everything distributed goes through
+:mod:`hcache_deepspeed_b200.comm` (NCCL on GPUs, gloo on CPU).
+"""
+from __future__ import annotations
+
+import os
+from typing import Callable, Dict, Iterable, Optional, Union
+
+import torch
+
+from .. import comm as dist
+from ..monitor.monitor import MonitorMaster
+from ..utils import groups
+from ..utils.logging import log_dist, logger
+from ..utils.timer import NoopTimer, SynchronizedWallClockTimer, ThroughputTimer
+from . import lr_schedules
+from .bf16_optimizer import BF16_Optimizer
+from .checkpoint_engine import NebulaCheckpointEngine, TorchCheckpointEngine
+from .config import (ADAGRAD_OPTIMIZER, ADAM_OPTIMIZER, ADAMW_OPTIMIZER, LAMB_OPTIMIZER, LION_OPTIMIZER,
+                     ONEBIT_ADAM_OPTIMIZER, ONEBIT_LAMB_OPTIMIZER, SGD_OPTIMIZER, ZERO_ONE_ADAM_OPTIMIZER, DeepSpeedConfig)
+from .dataloader import DeepSpeedDataLoader
+from .fp16.fused_optimizer import FP16_Optimizer, FP16_UnfusedOptimizer
+from .utils import clip_grad_norm_, flatten_dense_tensors, get_grad_norm, unflatten_dense_tensors
+from .zero.stage3 import DeepSpeedZeroOptimizer_Stage3
+from .zero.stage_1_and_2 import DeepSpeedZeroOptimizer
+
+FORWARD_MICRO_TIMER, FORWARD_GLOBAL_TIMER = "fwd_microstep", "fwd"
+BACKWARD_MICRO_TIMER, BACKWARD_GLOBAL_TIMER = "bwd_microstep", "bwd"
+STEP_MICRO_TIMER, STEP_GLOBAL_TIMER = "step_microstep", "step"
+MEMORY_OPT_ALLREDUCE_SIZE = 500000000
+
+
+class EngineTimers:
+    """Names of the wall-clock timers the engine drives."""
+
+    def __init__(self, enable_micro_timers: bool, enable_global_timers: bool):
+        self.forward_timers = [FORWARD_MICRO_TIMER] if enable_micro_timers else []
+        self.backward_timers = [BACKWARD_MICRO_TIMER] if enable_micro_timers else []
+        self.step_timers = [STEP_MICRO_TIMER] if enable_micro_timers else []
+        self.global_timers = [FORWARD_GLOBAL_TIMER, BACKWARD_GLOBAL_TIMER, STEP_GLOBAL_TIMER] if enable_global_timers else []
+        self.micro_timers = self.forward_timers + self.backward_timers + self.step_timers
+
+
+def _device_for(local_rank: int) -> torch.device:
+    if torch.cuda.is_available():
+        return torch.device("cuda", local_rank if local_rank >= 0 else 0)
+    return torch.device("cpu")
+
+
+class DeepSpeedEngine(torch.nn.Module):
+
+    def __init__(self, args=None, model: torch.nn.Module = None, optimizer=None, model_parameters=None, training_data=None,
+                 lr_scheduler=None, mpu=None, dist_init_required: Optional[bool] = None, collate_fn=None, config=None,
+                 config_class: Optional[DeepSpeedConfig] = None, mesh_device=None, dont_change_device: bool = False):
+        super().__init__()
+        assert model is not None, "deepspeed.initialize requires a model"
+        self.client_optimizer = optimizer
+        self.client_lr_scheduler = lr_scheduler
+        self.training_data = training_data
+        self.collate_fn = collate_fn
+        self.mpu = mpu
+        self.global_steps = 0
+        self.global_samples = 0
+        self.micro_steps = 0
+        self.skipped_steps = 0
+        self.gradient_average = True
+        self.warn_unscaled_loss = True
+        self.loaded_checkpoint_mp_world_size = None
+        self.loaded_checkpoint_dp_world_size = None
+        self.enable_backward_allreduce = True
+        self._is_gradient_accumulation_boundary = None
+        self.losses = None
+        self._global_grad_norm = None
+        self.dont_change_device = dont_change_device
+
+        if dist_init_required is None or dist_init_required:
+            if not dist.is_initialized() and int(os.environ.get("WORLD_SIZE", "1")) > 1:
+                dist.init_distributed()
+        self.local_rank = int(os.environ.get("LOCAL_RANK", getattr(args, "local_rank", 0) if args is not None else 0) or 0)
+        self.device = _device_for(self.local_rank)
+        if self.device.type == "cuda":
+            torch.cuda.set_device(self.device)
+        self.global_rank = dist.get_rank() if dist.is_initialized() else 0
+        self.world_size = dist.get_world_size() if dist.is_initialized() else 1
+
+        if mpu is not None:
+            groups.mpu = mpu
+        self._config = config_class if config_class is not None else DeepSpeedConfig(
+            config if config is not None else getattr(args, "deepspeed_config", None), mpu=mpu)
+        self._configure_groups()
+        self.dp_world_size = dist.get_world_size(group=self.data_parallel_group) if dist.is_initialized() else 1
+        self.mp_world_size = mpu.get_model_parallel_world_size() if mpu is not None else 1
+        self.seq_parallel_group = groups._get_sequence_parallel_group()
+        self.sequence_parallel_size = groups._get_sequence_parallel_world_size() if dist.is_initialized() else 1
+
+        if self._config.comms_config.enabled:
+            dist.configure(self._config)
+        self.monitor = MonitorMaster(self._config.monitor_config)
+        self.timers = SynchronizedWallClockTimer() if self.wall_clock_breakdown() else NoopTimer()
+        self.engine_timers = EngineTimers(self.wall_clock_breakdown(), self.wall_clock_breakdown())
+        self.tput_timer = ThroughputTimer(batch_size=self.train_batch_size(), steps_per_output=self.steps_per_print())
+
+        self._configure_module(model)
+        self.param_names = {p: n for n, p in self.module.named_parameters()}
+        self.optimizer = None
+        self.basic_optimizer = None
+        self.lr_scheduler = None
+        has_optimizer = optimizer is not None or self._config.optimizer_name is not None
+        if model_parameters is None:
+            model_parameters = [p for p in self.module.parameters() if p.requires_grad]
+        if has_optimizer:
+            self._configure_optimizer(optimizer, list(model_parameters))
+            self._configure_lr_scheduler(lr_scheduler)
+        elif self.zero_optimization_stage() == 3:
+            from .zero.stage3 import DeepSpeedZeRoOffload
+            self.optimizer = None
+            self._zero3_offload = DeepSpeedZeRoOffload(self.module, dp_process_group=self.data_parallel_group,
+                                                       param_persistence_threshold=self._config.zero_config.param_persistence_threshold,
+                                                       offload_param_config=self._config.zero_config.offload_param)
+        self.training_dataloader = self.deepspeed_io(training_data) if training_data is not None else None
+        self.checkpoint_engine = None
+        self._configure_checkpointing()
+        self.flops_profiler = None
+        if self._config.flops_profiler_config.enabled:
+            from ..profiling.flops_profiler.profiler import FlopsProfiler
+            self.flops_profiler = FlopsProfiler(self.module, self)
+        self.progressive_layer_drop = None
+        if self._config.pld_enabled:
+            from .progressive_layer_drop import ProgressiveLayerDrop
+            self.progressive_layer_drop = ProgressiveLayerDrop(theta=self._config.pld_config.theta,
+                                                               gamma=self._config.pld_config.gamma)
+        self.curriculum_scheduler_legacy = None
+        if self._config.curriculum_enabled_legacy:
+            from .data_pipeline.curriculum_scheduler import CurriculumScheduler
+            self.curriculum_scheduler_legacy = CurriculumScheduler(self._config.curriculum_params_legacy)
+        self.eigenvalue = None
+        if self._config.eigenvalue_enabled:
+            from .eigenvalue import Eigenvalue
+            ec = self._config.eigenvalue_config
+            self.eigenvalue = Eigenvalue(verbose=ec.verbose, max_iter=ec.max_iter, tol=ec.tol, stability=ec.stability,
+                                         gas_boundary_resolution=ec.gas_boundary_resolution, layer_name=ec.layer_name,
+                                         layer_num=ec.layer_num)
+        if self.global_rank == 0 and self._config.dump_state:
+            self._config.print("DeepSpeedEngine configuration")
+
+    # ------------------------------------------------------------------------------------------------
+    # configuration accessors (same names as the reference engine)
+    # ------------------------------------------------------------------------------------------------
+    def train_batch_size(self):
+        return self._config.train_batch_size
+
+    def train_micro_batch_size_per_gpu(self):
+        return self._config.train_micro_batch_size_per_gpu
+
+    def gradient_accumulation_steps(self):
+        return self._config.gradient_accumulation_steps
+
+    def set_train_batch_size(self, train_batch_size: int):
+        """Adjust the global batch size by changing the number of accumulation steps (micro-batch size is fixed)."""
+        per_step = self.train_micro_batch_size_per_gpu() * self.dp_world_size
+        if train_batch_size % per_step != 0:
+            raise ValueError("Train batch size must be divisible by micro-batch size * data parallelism")
+        self._config.train_batch_size = train_batch_size
+        self._config.gradient_accumulation_steps = train_batch_size // per_step
+
+    def set_train_micro_batch_size(self, micro_batch_size: int):
+        self._config.train_batch_size = micro_batch_size * self.gradient_accumulation_steps() * self.dp_world_size
+        self._config.train_micro_batch_size_per_gpu = micro_batch_size
+
+    def steps_per_print(self):
+        return self._config.steps_per_print
+
+    def wall_clock_breakdown(self):
+        return self._config.wall_clock_breakdown
+
+    def zero_optimization(self):
+        return self._config.zero_enabled
+
+    def zero_optimization_stage(self):
+        return self._config.zero_optimization_stage
+
+    def zero_cpu_offload(self):
+        o = self._config.zero_config.offload_optimizer
+        return o is not None and str(getattr(o.device, "value", o.device)) == "cpu"
+
+    def zero_offload_param(self):
+        return self._config.zero_config.offload_param
+
+    def fp16_enabled(self):
+        return self._config.fp16_enabled
+
+    def bfloat16_enabled(self):
+        return self._config.bfloat16_enabled
+
+    def amp_enabled(self):
+        return self._config.amp_enabled
+
+    def gradient_clipping(self):
+        return self._config.gradient_clipping
+
+    def dynamic_loss_scale(self):
+        return self._config.loss_scale == 0
+
+    def loss_scale(self):
+        return self._config.loss_scale
+
+    def optimizer_name(self):
+        return self.client_optimizer.__class__.__name__ if self.client_optimizer else self._config.optimizer_name
+
+    def optimizer_params(self):
+        return self._config.optimizer_params
+
+    def scheduler_name(self):
+        return self._config.scheduler_name
+
+    def scheduler_params(self):
+        return self._config.scheduler_params
+
+    def postscale_gradients(self):
+        return not self._config.prescale_gradients
+
+    def gradient_predivide_factor(self):
+        return self._config.gradient_predivide_factor
+
+    def communication_data_type(self):
+        return {None: None, "fp16": torch.float16, "bf16": torch.bfloat16, "fp32": torch.float32}.get(
+            self._config.communication_data_type, None)
+
+    def get_data_types(self):
+        model_dtype = torch.float16 if self.fp16_enabled() else torch.bfloat16 if self.bfloat16_enabled() else torch.float32
+        acc = {None: model_dtype if not self.bfloat16_enabled() else torch.float32, "fp32": torch.float32,
+               "fp16": torch.float16, "bf16": torch.bfloat16}[self._config.grad_accum_dtype]
+        return model_dtype, acc
+
+    @property
+    def config(self):
+        return self._config._param_dict
+
+    # ------------------------------------------------------------------------------------------------
+    def _configure_groups(self):
+        cfg = self._config
+        if not dist.is_initialized():
+            self.data_parallel_group = None
+            return
+        if self.mpu is not None:
+            self.data_parallel_group = self.mpu.get_data_parallel_group()
+        elif cfg.sequence_parallel_size > 1:
+            groups._create_model_parallel(1, cfg.sequence_parallel_size)
+            self.data_parallel_group = groups._get_sequence_data_parallel_group()
+        else:
+            self.data_parallel_group = groups._get_data_parallel_group()
+
+    def _configure_module(self, model: torch.nn.Module):
+        if self.fp16_enabled():
+            model = model.half()
+        elif self.bfloat16_enabled():
+            model = model.bfloat16()
+        if not self.dont_change_device:
+            from .zero.partition_parameters import is_zero_param
+            if not any(is_zero_param(p) for p in model.parameters()):
+                model = model.to(self.device)
+        self.module = model
+        self._broadcast_model()
+
+    def _broadcast_model(self):
+        if not dist.is_initialized() or self.dp_world_size_safe() == 1:
+            return
+        from .zero.partition_parameters import is_zero_param
+        src = dist.get_global_rank(self.data_parallel_group, 0)
+        for t in list(self.module.parameters()) + list(self.module.buffers()):
+            if is_zero_param(t) or not torch.is_tensor(t) or t.numel() == 0:
+                continue
+            if getattr(t, "allreduce", True) is False:  # expert parameters are not replicated over the dp group
+                continue
+            dist.broadcast(t.data, src, group=self.data_parallel_group)
+
+    def dp_world_size_safe(self):
+        return dist.get_world_size(group=self.data_parallel_group) if dist.is_initialized() else 1
+
+    # ------------------------------------------------------------------------------------------------
+    # optimizer
+    # ------------------------------------------------------------------------------------------------
+    def _configure_basic_optimizer(self, model_parameters):
+        name = self._config.optimizer_name
+        params = dict(self._config.optimizer_params)
+        params.pop("max_grad_norm", None)
+        if name in (ADAM_OPTIMIZER, ADAMW_OPTIMIZER):
+            torch_adam = params.pop("torch_adam", False)
+            adam_w_mode = params.pop("adam_w_mode", name == ADAMW_OPTIMIZER)
+            if self.zero_cpu_offload() and self._config.zero_force_ds_cpu_optimizer:
+                from ..ops.adam import DeepSpeedCPUAdam
+                return DeepSpeedCPUAdam(model_parameters, **params, adamw_mode=adam_w_mode)
+            if torch_adam:
+                cls = torch.optim.AdamW if adam_w_mode else torch.optim.Adam
+                return cls(model_parameters, **params)
+            from ..ops.adam import FusedAdam
+            return FusedAdam(model_parameters, **params, adam_w_mode=adam_w_mode)
+        if name == ADAGRAD_OPTIMIZER:
+            if self.zero_cpu_offload():
+                from ..ops.adagrad import DeepSpeedCPUAdagrad
+                return DeepSpeedCPUAdagrad(model_parameters, **params)
+            return torch.optim.Adagrad(model_parameters, **params)
+        if name == LAMB_OPTIMIZER:
+            from ..ops.lamb import FusedLamb
+            return FusedLamb(model_parameters, **params)
+        if name == LION_OPTIMIZER:
+            if self.zero_cpu_offload():
+                from ..ops.lion import DeepSpeedCPULion
+                return DeepSpeedCPULion(model_parameters, **params)
+            from ..ops.lion import FusedLion
+            return FusedLion(model_parameters, **params)
+        if name == SGD_OPTIMIZER:
+            return torch.optim.SGD(model_parameters, **params)
+        if name == ONEBIT_ADAM_OPTIMIZER:
+            from .fp16.onebit.adam import OnebitAdam
+            return OnebitAdam(model_parameters, self, **params)
+        if name == ZERO_ONE_ADAM_OPTIMIZER:
+            from .fp16.onebit.zoadam import ZeroOneAdam
+            return ZeroOneAdam(model_parameters, self, **params)
+        if name == ONEBIT_LAMB_OPTIMIZER:
+            from .fp16.onebit.lamb import OnebitLamb
+            return OnebitLamb(model_parameters, self, **params)
+        if isinstance(name, str) and hasattr(torch.optim, name):
+            return getattr(torch.optim, name)(model_parameters, **params)
+        raise ValueError(f"unknown optimizer type {name!r}")
+
+    def _configure_optimizer(self, client_optimizer, model_parameters):
+        if client_optimizer is None:
+            basic = self._configure_basic_optimizer(model_parameters)
+        elif isinstance(client_optimizer, torch.optim.Optimizer):
+            basic = client_optimizer
+        elif callable(client_optimizer):
+            basic = client_optimizer(model_parameters)
+        else:
+            raise TypeError("optimizer must be a torch.optim.Optimizer or a callable returning one")
+        self.basic_optimizer = basic
+        stage = self.zero_optimization_stage()
+        zc = self._config.zero_config
+        clip = self.gradient_clipping()
+        model_dtype, acc_dtype = self.get_data_types()
+        if stage in (1, 2):
+            self.optimizer = DeepSpeedZeroOptimizer(
+                basic, param_names=self.param_names, timers=self.timers, static_loss_scale=self.loss_scale() or 1.0,
+                dynamic_loss_scale=self.fp16_enabled() and self.dynamic_loss_scale(),
+                dynamic_loss_args=self._config.dynamic_loss_scale_args, contiguous_gradients=zc.contiguous_gradients,
+                reduce_bucket_size=zc.reduce_bucket_size, allgather_bucket_size=zc.allgather_bucket_size,
+                dp_process_group=self.data_parallel_group, reduce_scatter=zc.reduce_scatter, overlap_comm=zc.overlap_comm,
+                offload_optimizer_config=zc.offload_optimizer, mpu=self.mpu, clip_grad=clip,
+                gradient_accumulation_dtype=acc_dtype if self.bfloat16_enabled() else torch.float32,
+                communication_data_type=self._config.communication_data_type,
+                postscale_gradients=self.postscale_gradients(), gradient_predivide_factor=self.gradient_predivide_factor(),
+                gradient_accumulation_steps=self.gradient_accumulation_steps(), partition_grads=stage == 2,
+                round_robin_gradients=zc.round_robin_gradients, verbose=self.global_rank == 0)
+        elif stage == 3:
+            cls = DeepSpeedZeroOptimizer_Stage3
+            extra = {}
+            if zc.mics_shard_size > 0:
+                from .zero.mics import MiCS_Optimizer, create_mics_comm_groups
+                cls = MiCS_Optimizer
+                extra["mics_comm_groups"] = create_mics_comm_groups(zc.mics_shard_size, self.data_parallel_group, mpu=self.mpu)
+            self.optimizer = cls(
+                self.module, basic, param_names=self.param_names, timers=self.timers, ds_config=self._config,
+                static_loss_scale=self.loss_scale() or 1.0,
+                dynamic_loss_scale=self.fp16_enabled() and self.dynamic_loss_scale(),
+                dynamic_loss_args=self._config.dynamic_loss_scale_args, dp_process_group=self.data_parallel_group,
+                param_persistence_threshold=zc.param_persistence_threshold, offload_optimizer_config=zc.offload_optimizer,
+                offload_param_config=zc.offload_param, mpu=self.mpu, clip_grad=clip,
+                gradient_predivide_factor=self.gradient_predivide_factor(), verbose=self.global_rank == 0, **extra)
+        elif self.fp16_enabled():
+            dyn = self.dynamic_loss_scale()
+            if type(basic).__name__ in ("FusedLamb", "OnebitLamb"):
+                self.optimizer = FP16_UnfusedOptimizer(basic, self, static_loss_scale=self.loss_scale() or 1.0,
+                                                       dynamic_loss_scale=dyn,
+                                                       dynamic_loss_args=self._config.dynamic_loss_scale_args,
+                                                       mpu=self.mpu, clip_grad=clip)
+            else:
+                self.optimizer = FP16_Optimizer(basic, self, static_loss_scale=self.loss_scale() or 1.0,
+                                                dynamic_loss_scale=dyn, initial_dynamic_scale=self._config.initial_dynamic_scale,
+                                                dynamic_loss_args=self._config.dynamic_loss_scale_args, mpu=self.mpu,
+                                                clip_grad=clip)
+        elif self.bfloat16_enabled():
+            self.optimizer = BF16_Optimizer(basic, param_names=self.param_names, mpu=self.mpu, clip_grad=clip,
+                                            dp_process_group=self.data_parallel_group, timers=self.timers,
+                                            grad_acc_dtype=acc_dtype,
+                                            immediate_grad_update=self._config.bf16_config.immediate_grad_update)
+        else:
+            self.optimizer = basic
+        log_dist(f"DeepSpeed optimizer = {type(self.optimizer).__name__} over {type(basic).__name__}", ranks=[0])
+
+    def _configure_lr_scheduler(self, client_lr_scheduler):
+        if client_lr_scheduler is not None:
+            if callable(client_lr_scheduler) and not hasattr(client_lr_scheduler, "step"):
+                self.lr_scheduler = client_lr_scheduler(self.basic_optimizer)
+            else:
+                self.lr_scheduler = client_lr_scheduler
+        elif self._config.scheduler_name is not None:
+            cls = lr_schedules.get_lr_schedule_class(self._config.scheduler_name)
+            self.lr_scheduler = cls(self.basic_optimizer, **self._config.scheduler_params)
+        log_dist(f"DeepSpeed LR scheduler = {type(self.lr_scheduler).__name__ if self.lr_scheduler else None}", ranks=[0])
+
+    def _configure_checkpointing(self):
+        self.checkpoint_engine = TorchCheckpointEngine()
+        if (self.config.get("nebula") or {}).get("enabled"):
+            self.checkpoint_engine = NebulaCheckpointEngine(self.config.get("nebula"))
+        dp_rank = dist.get_rank(group=self.data_parallel_group) if dist.is_initialized() else 0
+        self.save_non_zero_checkpoint = dp_rank == 0
+        self.save_zero_checkpoint = self.zero_optimization() or (self.bfloat16_enabled() and self.optimizer is not None and
+                                                                 isinstance(self.optimizer, BF16_Optimizer))
+
+    # ------------------------------------------------------------------------------------------------
+    # data
+    # ------------------------------------------------------------------------------------------------
+    def deepspeed_io(self, dataset, batch_size=None, route="train", pin_memory=True, data_sampler=None, collate_fn=None,
+                     num_local_io_workers=None):
+        if not isinstance(dataset, torch.utils.data.Dataset):
+            raise ValueError("Training data must be a torch Dataset")
+        if batch_size is None:
+            batch_size = self.train_micro_batch_size_per_gpu()
+        dp_ws = self.dp_world_size
+        dp_rank = dist.get_rank(group=self.data_parallel_group) if dist.is_initialized() else 0
+        return DeepSpeedDataLoader(dataset=dataset, batch_size=batch_size, pin_memory=pin_memory,
+                                   collate_fn=collate_fn or self.collate_fn, local_rank=self.local_rank,
+                                   tput_timer=self.tput_timer if route == "train" else None,
+                                   num_local_io_workers=num_local_io_workers, data_sampler=data_sampler,
+                                   data_parallel_world_size=dp_ws, data_parallel_rank=dp_rank,
+                                   dataloader_drop_last=self._config.dataloader_drop_last)
+
+    # ------------------------------------------------------------------------------------------------
+    # train loop pieces
+    # ------------------------------------------------------------------------------------------------
+    def train(self, mode: bool = True):
+        self.warn_unscaled_loss = True
+        self.module.train(mode)
+        return self
+
+    def eval(self):
+        self.warn_unscaled_loss = True
+        self.module.train(False)
+        return self
+
+    def is_gradient_accumulation_boundary(self) -> bool:
+        if self._is_gradient_accumulation_boundary is None:
+            return (self.micro_steps + 1) % self.gradient_accumulation_steps() == 0
+        return self._is_gradient_accumulation_boundary
+
+    def set_gradient_accumulation_boundary(self, is_boundary: bool):
+        self._is_gradient_accumulation_boundary = is_boundary
+        if hasattr(self.optimizer, "is_gradient_accumulation_boundary"):
+            self.optimizer.is_gradient_accumulation_boundary = is_boundary
+
+    def _scale_loss_by_gas(self, loss):
+        gas = self.gradient_accumulation_steps()
+        if isinstance(loss, torch.Tensor):
+            return loss / gas
+        if isinstance(loss, (tuple, list)) and isinstance(loss[0], torch.Tensor):
+            return type(loss)(l / gas for l in loss)
+        if self.warn_unscaled_loss:
+            logger.warning(f"DeepSpeed unable to scale loss because of type: {type(loss)}")
+            self.warn_unscaled_loss = False
+        return loss
+
+    def forward(self, *inputs, **kwargs):
+        if self.flops_profiler is not None and self.global_steps == self._config.flops_profiler_config.profile_step and \
+                self.global_rank == 0 and self.micro_steps % self.gradient_accumulation_steps() == 0:
+            self.flops_profiler.start_profile(ignore_list=None)
+        if self.progressive_layer_drop is not None and self.module.training:
+            kwargs.update(self.progressive_layer_drop.get_state())
+        if self.curriculum_scheduler_legacy is not None and self.module.training:
+            self.curriculum_scheduler_legacy.update_difficulty(self.global_steps + 1)
+            if self._config.curriculum_params_legacy.get("curriculum_type") == "seqlen":
+                kwargs["curriculum_seqlen"] = self.curriculum_scheduler_legacy.get_current_difficulty()
+        self.timers(FORWARD_MICRO_TIMER).start()
+        self.timers(FORWARD_GLOBAL_TIMER).start()
+        if self.training_dataloader is None and self.module.training:
+            self.tput_timer.start()
+        loss = self.module(*inputs, **kwargs)
+        self.timers(FORWARD_MICRO_TIMER).stop()
+        self.timers(FORWARD_GLOBAL_TIMER).stop()
+        if self.flops_profiler is not None and self.flops_profiler.started:
+            fc = self._config.flops_profiler_config
+            self.flops_profiler.stop_profile()
+            self.flops_profiler.print_model_profile(profile_step=self.global_steps, module_depth=fc.module_depth,
+                                                    top_modules=fc.top_modules, detailed=fc.detailed,
+                                                    output_file=fc.output_file)
+            self.flops_profiler.end_profile()
+        return loss
+
+    def _uses_wrapper_backward(self) -> bool:
+        return isinstance(self.optimizer, (DeepSpeedZeroOptimizer, DeepSpeedZeroOptimizer_Stage3, FP16_Optimizer,
+                                           FP16_UnfusedOptimizer))
+
+    def backward(self, loss, retain_graph: bool = False, scale_wrt_gas: bool = True):
+        assert self.optimizer is not None or self.zero_optimization_stage() == 3, \
+            "must provide optimizer during init in order to use backward"
+        self.timers(BACKWARD_MICRO_TIMER).start()
+        self.timers(BACKWARD_GLOBAL_TIMER).start()
+        if self.gradient_accumulation_steps() > 1 and scale_wrt_gas:
+            loss = self._scale_loss_by_gas(loss.float())
+        if self.monitor.enabled and self.is_gradient_accumulation_boundary():
+            self.losses = loss.detach() if self.losses is None else self.losses + loss.detach()
+        elif self.monitor.enabled:
+            self.losses = loss.detach() if self.losses is None else self.losses + loss.detach()
+        if self._uses_wrapper_backward():
+            self.optimizer.backward(loss, retain_graph=retain_graph)
+        else:
+            if self.eigenvalue is not None:
+                loss.backward(create_graph=True, retain_graph=True)
+            else:
+                loss.backward(retain_graph=retain_graph)
+        if self.enable_backward_allreduce and self.is_gradient_accumulation_boundary():
+            self.allreduce_gradients()
+        self.timers(BACKWARD_MICRO_TIMER).stop()
+        self.timers(BACKWARD_GLOBAL_TIMER).stop()
+        return loss
+
+    def allreduce_gradients(self, bucket_size: int = MEMORY_OPT_ALLREDUCE_SIZE):
+        """Average gradients over the data-parallel group at the accumulation boundary. ZeRO optimizers own their
+        reduction (stage 1 at step, stage 2/3 per micro-batch); this is the plain-DP / fp16 / non-partitioned path."""
+        if isinstance(self.optimizer, (DeepSpeedZeroOptimizer, DeepSpeedZeroOptimizer_Stage3)):
+            return
+        if not dist.is_initialized() or self.dp_world_size == 1:
+            return
+        self.buffered_allreduce_fallback(elements_per_buffer=bucket_size)
+
+    def buffered_allreduce_fallback(self, grads=None, elements_per_buffer: int = MEMORY_OPT_ALLREDUCE_SIZE):
+        by_dtype: Dict[torch.dtype, list] = {}
+        expert: Dict[str, list] = {}
+        for p in self.module.parameters():
+            if not p.requires_grad:
+                continue
+            if p.grad is None:
+                p.grad = torch.zeros_like(p)  # every rank must contribute the same buckets
+            if getattr(p, "allreduce", True) is False and hasattr(p, "group_name"):
+                expert.setdefault(p.group_name, []).append(p.grad.data)
+            else:
+                by_dtype.setdefault(p.grad.dtype, []).append(p.grad.data)
+        for tensors in by_dtype.values():
+            self._allreduce_buckets(tensors, self.data_parallel_group, self.dp_world_size, elements_per_buffer)
+        for name, tensors in expert.items():  # expert grads average over the expert-data-parallel group only
+            g = groups._get_expert_data_parallel_group(name)
+            self._allreduce_buckets(tensors, g, dist.get_world_size(group=g), elements_per_buffer)
+
+    def _allreduce_buckets(self, tensors, group, ws, elements_per_buffer):
+        if ws == 1:
+            return
+        bucket, n = [], 0
+        for t in tensors + [None]:
+            if t is not None and (n + t.numel() <= elements_per_buffer or not bucket):
+                bucket.append(t)
+                n += t.numel()
+                continue
+            flat = flatten_dense_tensors(bucket)
+            if self._config.prescale_gradients:
+                flat.div_(self.gradient_predivide_factor())
+                dist.all_reduce(flat, group=group)
+                if self.gradient_predivide_factor() != ws:
+                    flat.mul_(self.gradient_predivide_factor() / ws)
+            else:
+                dist.all_reduce(flat, group=group)
+                flat.div_(ws)
+            for dst, src in zip(bucket, unflatten_dense_tensors(flat, bucket)):
+                dst.copy_(src)
+            bucket, n = ([t], t.numel()) if t is not None else ([], 0)
+
+    def clip_fp32_gradients(self):
+        clip_grad_norm_(parameters=self.module.parameters(), max_norm=self.gradient_clipping(), mpu=self.mpu)
+
+    def _take_model_step(self, lr_kwargs=None):
+        plain = self.optimizer is self.basic_optimizer
+        if plain:
+            self._global_grad_norm = get_grad_norm(self.module.parameters(), mpu=self.mpu)
+            if self.gradient_clipping() > 0.0:
+                self.clip_fp32_gradients()
+        self.optimizer.step()
+        if not plain and hasattr(self.optimizer, "get_global_grad_norm"):
+            self._global_grad_norm = self.optimizer.get_global_grad_norm()
+        overflow = bool(getattr(self.optimizer, "overflow", False))
+        if hasattr(self.optimizer, "zero_grad"):
+            self.optimizer.zero_grad()
+        if plain:
+            for p in self.module.parameters():
+                p.grad = None
+        if overflow:
+            self.skipped_steps += 1
+        elif self.lr_scheduler is not None:
+            try:
+                self.lr_scheduler.step(**(lr_kwargs or {}))
+            except TypeError:
+                self.lr_scheduler.step()
+        self.global_steps += 1
+        self.global_samples += self.train_batch_size()
+
+    def step(self, lr_kwargs=None):
+        assert self.optimizer is not None, "must provide optimizer during init in order to use step"
+        self.timers(STEP_MICRO_TIMER).start()
+        self.timers(STEP_GLOBAL_TIMER).start()
+        report = False
+        if self.is_gradient_accumulation_boundary():
+            self.gas_boundary_ctr = getattr(self, "gas_boundary_ctr", 0) + 1
+            if self.progressive_layer_drop is not None:
+                self.progressive_layer_drop.update_state(self.global_steps)
+            if self.eigenvalue is not None and self.gas_boundary_ctr % self.eigenvalue.gas_boundary_resolution == 0:
+                self.block_eigenvalue = self.eigenvalue.compute_eigenvalue(self.module, self.device)
+            self._take_model_step(lr_kwargs)
+            report = True
+        self.tput_timer.stop(global_step=self.is_gradient_accumulation_boundary(), report_speed=report)
+        self.timers(STEP_MICRO_TIMER).stop()
+        self.timers(STEP_GLOBAL_TIMER).stop()
+        if report:
+            if self.monitor.enabled and self.global_rank == 0:
+                events = [("Train/Samples/lr", self.get_lr()[0], self.global_samples)]
+                if self.losses is not None:
+                    events.append(("Train/Samples/train_loss", float(self.losses), self.global_samples))
+                if self.fp16_enabled() and hasattr(self.optimizer, "cur_scale"):
+                    events.append(("Train/Samples/loss_scale", self.optimizer.cur_scale, self.global_samples))
+                self.monitor.write_events(events)
+            self.losses = None
+            if self.steps_per_print() and self.global_steps % self.steps_per_print() == 0:
+                log_dist(f"step={self.global_steps}, skipped={self.skipped_steps}, lr={self.get_lr()}, "
+                         f"mom={self.get_mom()}", ranks=[0])
+                if self.wall_clock_breakdown():
+                    self.timers.log(self.engine_timers.global_timers, normalizer=self.steps_per_print() or 1)
+        self.micro_steps += 1
+
+    def no_sync(self):
+        """Context manager that suppresses gradient reduction in ``backward`` (ZeRO stages >= 2 cannot skip it)."""
+        assert self.zero_optimization_stage() < 2, "no_sync is incompatible with ZeRO stage 2/3 gradient partitioning"
+        engine = self
+
+        class _NoSync:
+            def __enter__(self_inner):
+                self_inner.prev = engine.enable_backward_allreduce
+                engine.enable_backward_allreduce = False
+
+            def __exit__(self_inner, *exc):
+                engine.enable_backward_allreduce = self_inner.prev
+                return False
+
+        return _NoSync()
+
+    def zero_grad(self):
+        for p in self.module.parameters():
+            p.grad = None
+
+    def get_lr(self):
+        return [g["lr"] for g in self.optimizer.param_groups] if self.optimizer is not None else []
+
+    def get_mom(self):
+        out = []
+        for g in (self.optimizer.param_groups if self.optimizer is not None else []):
+            out.append(g["betas"] if "betas" in g else g.get("momentum", 0.0))
+        return out
+
+    def get_type(self):
+        return [g.get("type") for g in self.optimizer.param_groups]
+
+    def get_global_grad_norm(self):
+        return self._global_grad_norm
+
+    def get_loss_scale(self):
+        return getattr(self.optimizer, "cur_scale", 1.0)
+
+    def was_step_applied(self) -> bool:
+        return not bool(getattr(self.optimizer, "overflow", False))
+
+    def get_batch_info(self):
+        return self.train_batch_size(), self.train_micro_batch_size_per_gpu(), self.gradient_accumulation_steps()
+
+    def destroy(self):
+        if isinstance(self.optimizer, DeepSpeedZeroOptimizer_Stage3):
+            self.optimizer.parameter_offload.destroy()
+
+    # ------------------------------------------------------------------------------------------------
+    # checkpointing
+    # ------------------------------------------------------------------------------------------------
+    def _mp_rank(self) -> int:
+        return self.mpu.get_model_parallel_rank() if self.mpu is not None else 0
+
+    def _get_ckpt_name(self, checkpoints_path, tag, mp_placeholder=None):
+        mp = mp_placeholder if mp_placeholder is not None else f"{self._mp_rank():02d}"
+        if self.zero_optimization_stage() == 3:
+            dp_rank = dist.get_rank(group=self.data_parallel_group) if dist.is_initialized() else 0
+            return os.path.join(checkpoints_path, str(tag), f"zero_pp_rank_{dp_rank}_mp_rank_{mp}_model_states.pt")
+        return os.path.join(checkpoints_path, str(tag), f"mp_rank_{mp}_model_states.pt")
+
+    def _get_zero_ckpt_name(self, checkpoints_path, tag, dp_rank=None):
+        if dp_rank is None:
+            dp_rank = dist.get_rank(group=self.data_parallel_group) if dist.is_initialized() else 0
+        prefix = "bf16_" if isinstance(self.optimizer, BF16_Optimizer) else ""
+        return os.path.join(checkpoints_path, str(tag), f"{prefix}zero_pp_rank_{dp_rank}_mp_rank_{self._mp_rank():02d}_optim_states.pt")
+
+    def module_state_dict(self, exclude_frozen_parameters: bool = False):
+        sd = self.module.state_dict()
+        if exclude_frozen_parameters:
+            frozen = {n for n, p in self.module.named_parameters() if not p.requires_grad}
+            sd = {k: v for k, v in sd.items() if k not in frozen}
+        return sd
+
+    def _checkpoint_tag_validation(self, tag):
+        if not self._config.checkpoint_tag_validation_enabled or not dist.is_initialized() or self.world_size == 1:
+            return
+        import hashlib
+        h = int(hashlib.sha1(str(tag).encode()).hexdigest()[:12], 16)
+        t_min = torch.tensor([float(h)], dtype=torch.float64, device=self.device if self.device.type == "cuda" else "cpu")
+        t_max = t_min.clone()
+        dist.all_reduce(t_min, op=dist.ReduceOp.MIN)
+        dist.all_reduce(t_max, op=dist.ReduceOp.MAX)
+        if float(t_min) != float(t_max):
+            msg = f"[rank={self.global_rank}] The checkpoint tag name '{tag}' is not consistent across all ranks."
+            if self._config.checkpoint_tag_validation_fail:
+                raise AssertionError(msg)
+            logger.warning(msg)
+
+    def save_checkpoint(self, save_dir, tag=None, client_state=None, save_latest: bool = True,
+                        exclude_frozen_parameters: bool = False):
+        client_state = client_state or {}
+        if tag is None:
+            tag = f"global_step{self.global_steps}"
+        tag = str(tag)
+        self._checkpoint_tag_validation(tag)
+        self.checkpoint_engine.create(tag)
+        if self.global_rank == 0:
+            self.checkpoint_engine.makedirs(os.path.join(save_dir, tag), exist_ok=True)
+        if dist.is_initialized():
+            dist.barrier()
+        if self.save_non_zero_checkpoint or self.zero_optimization_stage() == 3:
+            self._save_checkpoint(save_dir, tag, client_state, exclude_frozen_parameters)
+        if self.save_zero_checkpoint:
+            self._save_zero_checkpoint(save_dir, tag)
+        self.checkpoint_engine.commit(tag)
+        if dist.is_initialized():
+            dist.barrier()
+        if save_latest and self.global_rank == 0:
+            with open(os.path.join(save_dir, "latest"), "w") as f:
+                f.write(tag)
+        return True
+
+    def _save_checkpoint(self, save_dir, tag, client_state, exclude_frozen_parameters=False):
+        zero_wrapped = isinstance(self.optimizer, (DeepSpeedZeroOptimizer, DeepSpeedZeroOptimizer_Stage3))
+        if self.zero_optimization_stage() == 3:
+            module_sd = {}  # parameters live in the optimizer partitions
+            buffers = {k: v for k, v in self.module.state_dict().items() if k not in dict(self.module.named_parameters())}
+        else:
+            module_sd = self.module_state_dict(exclude_frozen_parameters)
+            buffers = None
+        state = dict(module=module_sd, buffer_names=list(dict(self.module.named_buffers()).keys()), buffers=buffers,
+                     optimizer=self.optimizer.state_dict() if (self.optimizer is not None and not zero_wrapped) else None,
+                     param_shapes=self.optimizer._param_shapes() if isinstance(self.optimizer, DeepSpeedZeroOptimizer) else None,
+                     lr_scheduler=self.lr_scheduler.state_dict() if self.lr_scheduler is not None else None,
+                     skipped_steps=self.skipped_steps, global_steps=self.global_steps, global_samples=self.global_samples,
+                     dp_world_size=self.dp_world_size, mp_world_size=self.mp_world_size,
+                     ds_config=self._config._param_dict, ds_version=_version())
+        state.update(client_state)
+        self.checkpoint_engine.save(state, self._get_ckpt_name(save_dir, tag))
+
+    def _save_zero_checkpoint(self, save_dir, tag):
+        sd = dict(optimizer_state_dict=self.optimizer.state_dict(), ds_config=self._config._param_dict, ds_version=_version())
+        self.checkpoint_engine.save(sd, self._get_zero_ckpt_name(save_dir, tag))
+
+    def load_checkpoint(self, load_dir, tag=None, load_module_strict: bool = True, load_optimizer_states: bool = True,
+                        load_lr_scheduler_states: bool = True, load_module_only: bool = False, custom_load_fn=None):
+        if tag is None:
+            latest = os.path.join(load_dir, "latest")
+            if not os.path.isfile(latest):
+                logger.warning(f"Unable to find latest file at {latest}, if trying to load latest checkpoint please "
+                               "ensure this file exists or pass an explicit checkpoint tag when loading a checkpoint.")
+                return None, None
+            with open(latest) as f:
+                tag = f.read().strip()
+        path = self._get_ckpt_name(load_dir, tag)
+        if not os.path.exists(path):
+            logger.warning(f"Client provided checkpoint load path: {path} does not exist")
+            return None, None
+        ckpt = self.checkpoint_engine.load(path, map_location="cpu")
+        if self.zero_optimization_stage() != 3:
+            if custom_load_fn is not None:
+                custom_load_fn(src=ckpt["module"], dst=self.module)
+            else:
+                self.module.load_state_dict(ckpt["module"], strict=load_module_strict)
+        elif ckpt.get("buffers"):
+            own = dict(self.module.named_buffers())
+            for k, v in ckpt["buffers"].items():
+                if k in own:
+                    own[k].data.copy_(v)
+        self.loaded_checkpoint_dp_world_size = ckpt.get("dp_world_size")
+        self.loaded_checkpoint_mp_world_size = ckpt.get("mp_world_size")
+        if not load_module_only:
+            self.global_steps = ckpt.get("global_steps", 0)
+            self.global_samples = ckpt.get("global_samples", self.global_steps * self.train_batch_size())
+            self.skipped_steps = ckpt.get("skipped_steps", 0)
+            zero_wrapped = isinstance(self.optimizer, (DeepSpeedZeroOptimizer, DeepSpeedZeroOptimizer_Stage3))
+            if zero_wrapped:
+                zpath = self._get_zero_ckpt_name(load_dir, tag)
+                if os.path.exists(zpath):
+                    zsd = self.checkpoint_engine.load(zpath, map_location="cpu")
+                    self.optimizer.load_state_dict(zsd["optimizer_state_dict"], load_optimizer_states=load_optimizer_states)
+                elif load_optimizer_states:
+                    logger.warning(f"ZeRO optimizer state {zpath} not found; optimizer state was not restored")
+            elif load_optimizer_states and self.optimizer is not None and ckpt.get("optimizer") is not None:
+                self.optimizer.load_state_dict(ckpt["optimizer"])
+            if zero_wrapped and not load_optimizer_states and hasattr(self.optimizer, "refresh_fp32_params"):
+                self.optimizer.refresh_fp32_params()
+            if load_lr_scheduler_states and self.lr_scheduler is not None and ckpt.get("lr_scheduler") is not None:
+                self.lr_scheduler.load_state_dict(ckpt["lr_scheduler"])
+        elif hasattr(self.optimizer, "refresh_fp32_params"):
+            self.optimizer.refresh_fp32_params()
+        reserved = {"module", "buffer_names", "buffers", "optimizer", "param_shapes", "lr_scheduler", "skipped_steps",
+                    "global_steps", "global_samples", "dp_world_size", "mp_world_size", "ds_config", "ds_version"}
+        client_state = {k: v for k, v in ckpt.items() if k not in reserved}
+        return os.path.join(load_dir, str(tag)), client_state
+
+    def _zero3_consolidated_16bit_state_dict(self, exclude_frozen_parameters: bool = False):
+        from .zero.partition_parameters import GatheredParameters
+        sd = {}
+        for name, p in self.module.named_parameters():
+            if exclude_frozen_parameters and not p.requires_grad:
+                continue
+            with GatheredParameters([p]):
+                if self.global_rank == 0:
+                    sd[name] = p.data.detach().cpu().clone()
+        for name, b in self.module.named_buffers():
+            if self.global_rank == 0:
+                sd[name] = b.detach().cpu().clone()
+        return sd if self.global_rank == 0 else None
+
+    def save_16bit_model(self, save_dir, save_filename="pytorch_model.bin", exclude_frozen_parameters: bool = False):
+        """Write a consolidated 16-bit ``state_dict`` from rank 0 (gathers ZeRO-3 partitions)."""
+        if self.zero_optimization_stage() == 3:
+            sd = self._zero3_consolidated_16bit_state_dict(exclude_frozen_parameters)
+        else:
+            sd = self.module_state_dict(exclude_frozen_parameters)
+        if self.global_rank == 0:
+            os.makedirs(save_dir, exist_ok=True)
+            self.checkpoint_engine.save(sd, os.path.join(save_dir, save_filename))
+        return True
+
+    save_fp16_model = save_16bit_model
+
+
+def _version() -> str:
+    from ..version import __version__
+    return __version__
+
+
+def initialize(args=None, model: torch.nn.Module = None, optimizer=None, model_parameters=None, training_data=None,
+               lr_scheduler=None, distributed_port: int = 29500, mpu=None, dist_init_required: Optional[bool] = None,
+               collate_fn=None, config=None, mesh_param=None, config_params=None):
+    """Returns ``(engine, optimizer, training_dataloader, lr_scheduler)`` — ``deepspeed.initialize``
+    (``deepspeed/__init__.py:69-235``). ``config`` is a dict or a JSON path (``args.deepspeed_config`` also works)."""
+    assert model is not None, "deepspeed.initialize requires a model"
+    if config is None:
+        config = config_params
+    if config is None and args is not None:
+        config = getattr(args, "deepspeed_config", None) or getattr(args, "deepscale_config", None)
+    assert config is not None, "DeepSpeed requires --deepspeed_config to specify configuration file"
+    if not dist.is_initialized() and int(os.environ.get("WORLD_SIZE", "1")) > 1 and dist_init_required is not False:
+        dist.init_distributed(distributed_port=distributed_port)
+    from .pipe.module import PipelineModule
+    cfg = DeepSpeedConfig(config, mpu=mpu if not isinstance(model, PipelineModule) else model.mpu())
+    if isinstance(model, PipelineModule):
+        from .pipe.engine import PipelineEngine
+        engine = PipelineEngine(args=args, model=model, optimizer=optimizer, model_parameters=model_parameters,
+                                training_data=training_data, lr_scheduler=lr_scheduler, mpu=model.mpu(),
+                                dist_init_required=dist_init_required, collate_fn=collate_fn, config=config,
+                                config_class=cfg)
+    elif cfg.hybrid_engine.get("enabled", False):
+        from .hybrid_engine import DeepSpeedHybridEngine
+        engine = DeepSpeedHybridEngine(args=args, model=model, optimizer=optimizer, model_parameters=model_parameters,
+                                       training_data=training_data, lr_scheduler=lr_scheduler, mpu=mpu,
+                                       dist_init_required=dist_init_required, collate_fn=collate_fn, config=config,
+                                       config_class=cfg)
+    else:
+        engine = DeepSpeedEngine(args=args, model=model, optimizer=optimizer, model_parameters=model_parameters,
+                                 training_data=training_data, lr_scheduler=lr_scheduler, mpu=mpu,
+                                 dist_init_required=dist_init_required, collate_fn=collate_fn, config=config,
+                                 config_class=cfg)
+    return engine, engine.optimizer, engine.training_dataloader, engine.lr_scheduler

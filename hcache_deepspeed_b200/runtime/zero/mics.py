@@ -1,0 +1,84 @@
+"""MiCS: ZeRO-3 with parameters sharded inside a *sub-group* of ``mics_shard_size`` ranks and replicated across
+sub-groups (gathers stay inside a node / NVSwitch domain; gradients are reduced inside the shard group and then
+all-reduced across replicas). Reference: ``deepspeed/runtime/zero/mics.py`` (MiCS_Init :62, MiCS_Optimizer :358),
+``mics_utils.py`` (group creation)."""
+from __future__ import annotations
+
+from dataclasses import dataclass
+from typing import List, Optional
+
+import torch
+
+from ... import comm as dist
+from .partition_parameters import Init
+from .stage3 import DeepSpeedZeroOptimizer_Stage3
+
+
+@dataclass
+class MiCS_CommGroups:
+    param_shard_group: object = None
+    param_shard_size: int = -1
+    param_shard_rank: int = -1
+    param_repli_group: object = None
+    param_repli_size: int = -1
+    param_repli_rank: int = -1
+    param_intra_node_group: object = None
+    param_inter_node_shard_group: object = None
+
+
+def mics_group_ranks(world_size: int, shard_size: int):
+    """(shard groups, replicate groups): consecutive ranks shard, same-offset ranks replicate."""
+    assert world_size % shard_size == 0, "world size must be divisible by mics_shard_size"
+    shard = [list(range(i, i + shard_size)) for i in range(0, world_size, shard_size)]
+    repl = [list(range(o, world_size, shard_size)) for o in range(shard_size)]
+    return shard, repl
+
+
+def create_mics_comm_groups(shard_size: int, dp_group=None, hierarchical_allgather: bool = False, mpu=None) -> MiCS_CommGroups:
+    ws, me = dist.get_world_size(), dist.get_rank()
+    shard, repl = mics_group_ranks(ws, shard_size)
+    g = MiCS_CommGroups()
+    for ranks in shard:
+        grp = dist.new_group(ranks)
+        if me in ranks:
+            g.param_shard_group, g.param_shard_size, g.param_shard_rank = grp, len(ranks), ranks.index(me)
+    for ranks in repl:
+        grp = dist.new_group(ranks)
+        if me in ranks:
+            g.param_repli_group, g.param_repli_size, g.param_repli_rank = grp, len(ranks), ranks.index(me)
+    return g
+
+
+class MiCS_Init(Init):
+
+    def __init__(self, module=None, data_parallel_group=None, sequence_data_parallel_group=None, mem_efficient_linear=True,
+                 remote_device=None, pin_memory=False, config_dict_or_path=None, config=None, enabled=True, dtype=None,
+                 mpu=None):
+        cfg = config_dict_or_path if config_dict_or_path is not None else config
+        shard = int(((cfg or {}).get("zero_optimization") or {}).get("mics_shard_size", -1)) if isinstance(cfg, dict) else -1
+        self.mics_comm_groups = None
+        group = data_parallel_group
+        if enabled and shard > 0 and dist.is_initialized():
+            self.mics_comm_groups = create_mics_comm_groups(shard, data_parallel_group, mpu=mpu)
+            group = self.mics_comm_groups.param_shard_group
+        super().__init__(module=module, data_parallel_group=group, remote_device=remote_device, pin_memory=pin_memory,
+                         config_dict_or_path=cfg, enabled=enabled, dtype=dtype, mpu=mpu)
+
+
+class MiCS_Optimizer(DeepSpeedZeroOptimizer_Stage3):
+    """Stage-3 optimizer over the shard group, plus a gradient all-reduce across replica groups before the step."""
+
+    def __init__(self, module, init_optimizer, *args, mics_comm_groups: Optional[MiCS_CommGroups] = None, **kwargs):
+        self.mics_comm_groups = mics_comm_groups
+        if mics_comm_groups is not None:
+            kwargs["dp_process_group"] = mics_comm_groups.param_shard_group
+        super().__init__(module, init_optimizer, *args, **kwargs)
+
+    @torch.no_grad()
+    def step(self, closure=None):
+        g = self.mics_comm_groups
+        if g is not None and g.param_repli_size > 1:
+            for t in self.grad_partitions.values():
+                dist.all_reduce(t, group=g.param_repli_group)
+                t.div_(g.param_repli_size)
+        return super().step(closure)

@@ -1,0 +1,291 @@
+"""ZeRO-3 parameter partitioning: ``zero.Init`` converts every parameter of a module into a *partitioned parameter*
+whose full tensor exists only while it is needed; ``GatheredParameters`` temporarily reassembles parameters.
+
+Each converted ``torch.nn.Parameter`` carries:
+  ``ds_id``, ``ds_shape``, ``ds_numel``, ``ds_tensor`` (this rank's padded 1-D slice, optionally in pinned host
+  memory with ``remote_device='cpu'``), ``ds_status`` (:class:`ZeroParamStatus`), ``ds_persist`` (small parameters
+  stay gathered), ``ds_process_group`` and the methods ``all_gather()``, ``partition()``, ``partition_numel()``.
+While partitioned, ``param.data`` is an empty tensor. Gathering is one ``all_gather_into_tensor`` per parameter
+(or per coalesced list via :func:`all_gather_params`).
+Reference: ``deepspeed/runtime/zero/partition_parameters.py`` (Init :816, _convert_to_deepspeed_param :1107,
+GatheredParameters :2165, ZeroParamStatus :215).
+"""
+from __future__ import annotations
+
+import itertools
+from enum import Enum
+from typing import Iterable, List, Optional
+
+import torch
+
+from ... import comm as dist
+
+_param_id = itertools.count()
+
+
+class ZeroParamStatus(Enum):
+    AVAILABLE = 1      # full tensor present
+    NOT_AVAILABLE = 2  # only the local slice exists
+    INFLIGHT = 3       # gather issued
+
+
+class ZeroParamType(Enum):
+    NORMAL = 1
+    PARTITIONED = 2
+    REMOTE = 3
+
+
+def is_zero_param(p) -> bool:
+    return hasattr(p, "ds_id")
+
+
+def _group_info(group):
+    if dist.is_initialized():
+        return dist.get_world_size(group=group), dist.get_rank(group=group)
+    return 1, 0
+
+
+def _convert(param: torch.nn.Parameter, group, remote_device: Optional[str], pin_memory: bool, persistence_threshold: int,
+             dtype: Optional[torch.dtype]):
+    if is_zero_param(param):
+        return
+    ws, rank = _group_info(group)
+    if dtype is not None and param.dtype.is_floating_point and param.dtype != dtype:
+        param.data = param.data.to(dtype)
+    param.ds_id = next(_param_id)
+    param.ds_shape = param.data.shape
+    param.ds_numel = param.data.numel()
+    param.ds_process_group = group
+    param.ds_persist = param.ds_numel <= persistence_threshold
+    param.ds_active_sub_modules = set()
+    param.ds_param_type = ZeroParamType.PARTITIONED
+    psize = (param.ds_numel + ws - 1) // ws
+    param.ds_partition_numel = psize
+    flat = param.data.contiguous().view(-1)
+    lo, hi = rank * psize, min(param.ds_numel, (rank + 1) * psize)
+    part = torch.zeros(psize, dtype=flat.dtype, device=flat.device)
+    if lo < hi:
+        part[:hi - lo].copy_(flat[lo:hi])
+    if remote_device in ("cpu", "nvme"):
+        part = part.cpu()
+        if pin_memory and torch.cuda.is_available():
+            part = part.pin_memory()
+    param.ds_tensor = part
+    param.ds_tensor.ds_numel = psize
+    param.ds_device = flat.device
+    param.ds_status = ZeroParamStatus.AVAILABLE
+
+    def all_gather(param_list: Optional[List] = None, async_op: bool = False, hierarchy: int = 0):
+        all_gather_params(param_list if param_list is not None else [param])
+
+    def partition(param_list: Optional[List] = None, hierarchy: int = 0, has_been_updated: bool = False):
+        for p in (param_list if param_list is not None else [param]):
+            _partition_param(p, has_been_updated)
+
+    def partition_numel():
+        return param.ds_tensor.ds_numel
+
+    def padding_size():
+        return psize * ws - param.ds_numel
+
+    def ds_summary():
+        return {"id": param.ds_id, "status": param.ds_status.name, "numel": param.numel(), "ds_numel": param.ds_numel,
+                "shape": tuple(param.shape), "ds_shape": tuple(param.ds_shape), "requires_grad": param.requires_grad,
+                "persist": param.ds_persist, "device": str(param.device)}
+
+    param.all_gather, param.partition, param.partition_numel = all_gather, partition, partition_numel
+    param.padding_size, param.ds_summary = padding_size, ds_summary
+    if not param.ds_persist:
+        _partition_param(param, has_been_updated=False)
+
+
+@torch.no_grad()
+def _partition_param(p, has_been_updated: bool = False):
+    """Release the full tensor (first writing this rank's slice back if the full tensor was modified)."""
+    if p.ds_status != ZeroParamStatus.AVAILABLE:
+        return
+    if has_been_updated:
+        ws, rank = _group_info(p.ds_process_group)
+        psize = p.ds_partition_numel
+        flat = p.data.contiguous().view(-1)
+        lo, hi = rank * psize, min(p.ds_numel, (rank + 1) * psize)
+        if lo < hi:
+            p.ds_tensor[:hi - lo].copy_(flat[lo:hi])
+    if p.ds_persist:
+        return
+    p.data = torch.empty(0, dtype=p.dtype, device=p.ds_device)
+    p.ds_status = ZeroParamStatus.NOT_AVAILABLE
+
+
+@torch.no_grad()
+def all_gather_params(params: Iterable) -> None:
+    """Make the full tensors of ``params`` available (no-op for those that already are)."""
+    for p in params:
+        if not is_zero_param(p) or p.ds_status == ZeroParamStatus.AVAILABLE:
+            continue
+        ws, _ = _group_info(p.ds_process_group)
+        psize = p.ds_partition_numel
+        local = p.ds_tensor.to(p.ds_device, non_blocking=True)
+        if ws == 1:
+            full = local.clone()
+        else:
+            full = torch.empty(psize * ws, dtype=local.dtype, device=p.ds_device)
+            p.ds_status = ZeroParamStatus.INFLIGHT
+            dist.all_gather_into_tensor(full, local.contiguous(), group=p.ds_process_group)
+        p.data = full.narrow(0, 0, p.ds_numel).view(p.ds_shape)
+        p.ds_status = ZeroParamStatus.AVAILABLE
+
+
+class Init:
+    """Context manager: modules constructed inside are partitioned as they are created (``module=...`` converts an
+    existing one). ``remote_device`` ('cpu') keeps slices in host memory, ``pin_memory`` pins them."""
+    _active = 0
+
+    def __init__(self, module: Optional[torch.nn.Module] = None, data_parallel_group=None, mem_efficient_linear: bool = True,
+                 remote_device: Optional[str] = None, pin_memory: bool = False, config_dict_or_path=None, config=None,
+                 enabled: bool = True, dtype: Optional[torch.dtype] = None, mpu=None, zero_param_parallel_group=None,
+                 zero_quantized_weights: bool = False, zero_quantized_nontrainable_weights: bool = False,
+                 sequence_data_parallel_group=None, param_swapper=None):
+        cfg = config_dict_or_path if config_dict_or_path is not None else config
+        zc = {}
+        if isinstance(cfg, dict):
+            zc = cfg.get("zero_optimization", {}) or {}
+            if dtype is None:
+                dtype = torch.float16 if (cfg.get("fp16") or {}).get("enabled") else \
+                    torch.bfloat16 if (cfg.get("bf16") or {}).get("enabled") else None
+            off = zc.get("offload_param") or {}
+            if remote_device is None and off.get("device") in ("cpu", "nvme"):
+                remote_device, pin_memory = off["device"], bool(off.get("pin_memory", pin_memory))
+        self.enabled = enabled
+        self.group = data_parallel_group if data_parallel_group is not None else sequence_data_parallel_group
+        self.remote_device, self.pin_memory, self.dtype = remote_device, pin_memory, dtype
+        self.persistence_threshold = int(zc.get("stage3_param_persistence_threshold", zc.get("param_persistence_threshold", 0)))
+        self._wrapped = []
+        if module is not None and enabled:
+            self._convert_module(module)
+
+    def _convert_module(self, module: torch.nn.Module):
+        for p in module.parameters(recurse=True):
+            _convert(p, self.group, self.remote_device, self.pin_memory, self.persistence_threshold, self.dtype)
+
+    @staticmethod
+    def _all_subclasses(cls):
+        seen, stack = set(), [cls]
+        while stack:
+            c = stack.pop()
+            for sub in c.__subclasses__():
+                if sub not in seen:
+                    seen.add(sub)
+                    stack.append(sub)
+        return seen
+
+    def __enter__(self):
+        """Wrap ``__init__`` of every ``nn.Module`` subclass: when a module's constructor returns, the parameters it
+        registered directly are partitioned (children were handled by their own constructors), so initialisers that run
+        inside ``__init__`` still see full tensors."""
+        if not self.enabled:
+            return self
+        Init._active += 1
+        if Init._active > 1:
+            return self
+        ctx = self
+        self._wrapped = []
+
+        def wrap(cls):
+            orig = cls.__dict__.get("__init__")
+            if orig is None or getattr(orig, "_ds_zero_wrapped", False):
+                return
+            import functools
+
+            @functools.wraps(orig)
+            def init(mod, *a, **k):
+                mod._ds_init_depth = getattr(mod, "_ds_init_depth", 0) + 1
+                try:
+                    orig(mod, *a, **k)
+                finally:
+                    mod._ds_init_depth -= 1
+                if mod._ds_init_depth == 0 and Init._active > 0:
+                    for p in mod.parameters(recurse=False):
+                        _convert(p, ctx.group, ctx.remote_device, ctx.pin_memory, ctx.persistence_threshold, ctx.dtype)
+
+            init._ds_zero_wrapped = True
+            cls.__init__ = init
+            self._wrapped.append((cls, orig))
+
+        for cls in self._all_subclasses(torch.nn.Module):
+            wrap(cls)
+        return self
+
+    def __exit__(self, *exc):
+        if not self.enabled:
+            return False
+        Init._active -= 1
+        if Init._active == 0:
+            for cls, orig in self._wrapped:
+                cls.__init__ = orig
+            self._wrapped = []
+        return False
+
+
+class GatheredParameters:
+    """Temporarily gather ``params``; with ``modifier_rank`` set, that rank's in-place modifications are broadcast and
+    written back to every rank's slice on exit."""
+
+    def __init__(self, params, modifier_rank: Optional[int] = None, fwd_module: Optional[torch.nn.Module] = None,
+                 enabled: bool = True):
+        if isinstance(params, torch.nn.Module):
+            params = list(params.parameters())
+        elif isinstance(params, torch.Tensor):
+            params = [params]
+        self.params = [p for p in (params or []) if is_zero_param(p)]
+        self.enabled = enabled and len(self.params) > 0
+        self.src_rank = modifier_rank
+        self._was_available = []
+
+    def __enter__(self):
+        if not self.enabled:
+            return
+        self._was_available = [p.ds_status == ZeroParamStatus.AVAILABLE for p in self.params]
+        all_gather_params(self.params)
+
+    def __exit__(self, *exc):
+        if not self.enabled:
+            return False
+        if self.src_rank is not None and dist.is_initialized():
+            for p in self.params:
+                if dist.get_world_size(group=p.ds_process_group) > 1:
+                    dist.broadcast(p.data, dist.get_global_rank(p.ds_process_group, self.src_rank), group=p.ds_process_group)
+        for p, was in zip(self.params, self._was_available):
+            if self.src_rank is not None:
+                _partition_param(p, has_been_updated=True)
+                if was and p.ds_status != ZeroParamStatus.AVAILABLE:
+                    all_gather_params([p])
+            elif not was:
+                _partition_param(p, has_been_updated=False)
+        return False
+
+
+_external_params = {}
+
+
+def register_external_parameter(module: torch.nn.Module, parameter: torch.nn.Parameter):
+    """Declare that ``module``'s forward uses ``parameter`` owned by another module, so the stage-3 hooks gather it."""
+    if not isinstance(parameter, torch.nn.Parameter):
+        raise RuntimeError("Parameter is not a torch.nn.Parameter")
+    _external_params.setdefault(id(module), {})[id(parameter)] = parameter
+    if not hasattr(module, "_external_params"):
+        module._external_params = {}
+    module._external_params[id(parameter)] = parameter
+
+
+def unregister_external_parameter(module: torch.nn.Module, parameter: torch.nn.Parameter):
+    if hasattr(module, "_external_params"):
+        module._external_params.pop(id(parameter), None)
+
+
+def shutdown_init_context():
+    pass
+
+
+def restore_init_context():
+    pass

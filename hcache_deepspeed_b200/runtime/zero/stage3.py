@@ -1,0 +1,358 @@
+"""ZeRO stage 3: parameters, gradients and optimizer state are all partitioned over the data-parallel group.
+
+* ``DeepSpeedZeRoOffload`` installs module hooks: before a (sub)module's forward / backward its own parameters are
+  all-gathered, afterwards they are released again (parameters below ``param_persistence_threshold`` stay resident).
+  After a module's backward the full gradients are reduce-scattered into fp32 accumulators that cover only the
+  owned slice.
+* ``DeepSpeedZeroOptimizer_Stage3`` keeps an fp32 master copy of each owned slice (device or host memory), runs the
+  wrapped optimizer on those and writes the result back into the 16-bit slices; no parameter all-gather happens at
+  step time — the next forward fetches what it needs.
+
+Reference: ``deepspeed/runtime/zero/stage3.py`` (:73 optimizer, step :2040), ``parameter_offload.py``
+(DeepSpeedZeRoOffload :87, hooks :239-437), ``partitioned_param_coordinator.py`` (fetch/release/prefetch order).
+"""
+from __future__ import annotations
+
+import math
+from typing import List, Optional
+
+import torch
+
+from ... import comm as dist
+from ...utils.logging import logger
+from ..fp16.loss_scaler import CreateLossScaler
+from .partition_parameters import (Init, ZeroParamStatus, _partition_param, all_gather_params, is_zero_param)
+
+
+class DeepSpeedZeRoOffload:
+    """Fetch / release orchestration through module hooks."""
+
+    def __init__(self, module: torch.nn.Module, timers=None, ds_config=None, overlap_comm: bool = True,
+                 prefetch_bucket_size: int = 0, max_reuse_distance: int = 0, max_live_parameters: int = 0,
+                 param_persistence_threshold: int = 100000, model_persistence_threshold: int = 2 ** 62,
+                 dp_process_group=None, offload_param_config=None, mpu=None, zero_param_parallel_group=None,
+                 zero_quantized_weights=False, zero_quantized_nontrainable_weights=False,
+                 zero_module_granularity_threshold=0, log_trace_cache_warnings=False, dtype=None):
+        self.module = module
+        self.dp_process_group = dp_process_group
+        remote = None
+        pin = False
+        if offload_param_config is not None and str(getattr(offload_param_config, "device", "none")).split(".")[-1] in ("cpu", "nvme"):
+            remote, pin = "cpu", bool(getattr(offload_param_config, "pin_memory", False))
+        init = Init(data_parallel_group=dp_process_group, remote_device=remote, pin_memory=pin, dtype=dtype, enabled=True)
+        init.persistence_threshold = param_persistence_threshold
+        init._convert_module(module)
+        self.hooks = []
+        self.reduce_fn = None  # set by the optimizer: called with a list of params whose .grad is complete
+        self._install(module)
+
+    @staticmethod
+    def _own_params(m: torch.nn.Module) -> List[torch.nn.Parameter]:
+        ps = [p for p in m.parameters(recurse=False) if is_zero_param(p)]
+        ps += [p for p in getattr(m, "_external_params", {}).values() if is_zero_param(p)]
+        return ps
+
+    def _install(self, root: torch.nn.Module):
+        for m in root.modules():
+            if not self._own_params(m):
+                continue
+            self.hooks.append(m.register_forward_pre_hook(self._pre_forward))
+            self.hooks.append(m.register_forward_hook(self._post_forward))
+            self.hooks.append(m.register_full_backward_pre_hook(self._pre_backward))
+        # a parameter's gradient is final when its AccumulateGrad node has run — which can be after the owning module's
+        # backward hook — so reduction + release hang on the per-parameter post-accumulate hook
+        for p in root.parameters():
+            if is_zero_param(p) and p.requires_grad:
+                self.hooks.append(p.register_post_accumulate_grad_hook(self._post_accumulate))
+
+    def _pre_forward(self, m, args):
+        ps = self._own_params(m)
+        all_gather_params(ps)
+        for p in ps:
+            p.ds_active_sub_modules.add(id(m))
+
+    def _post_forward(self, m, args, out):
+        self._release(m)
+
+    def _pre_backward(self, m, grad_out):
+        ps = self._own_params(m)
+        all_gather_params(ps)
+        for p in ps:
+            p.ds_active_sub_modules.add(id(m))
+
+    def _post_accumulate(self, p):
+        if self.reduce_fn is not None:
+            self.reduce_fn([p])
+        p.ds_active_sub_modules.clear()
+        if not p.ds_persist:
+            _partition_param(p, has_been_updated=False)
+
+    def _release(self, m):
+        for p in self._own_params(m):
+            p.ds_active_sub_modules.discard(id(m))
+            if not p.ds_active_sub_modules and not p.ds_persist:
+                _partition_param(p, has_been_updated=False)
+
+    def destroy(self):
+        for h in self.hooks:
+            h.remove()
+        self.hooks = []
+
+    def get_param_coordinator(self, training=True):
+        return self
+
+
+class DeepSpeedZeroOptimizer_Stage3:
+
+    def __init__(self, module: torch.nn.Module, init_optimizer, param_names=None, timers=None, ds_config=None,
+                 static_loss_scale: float = 1.0, dynamic_loss_scale: bool = False, dynamic_loss_args=None,
+                 verbose: bool = True, contiguous_gradients: bool = True, reduce_bucket_size: int = 500000000,
+                 prefetch_bucket_size: int = 50000000, max_reuse_distance: int = 1000000000,
+                 max_live_parameters: int = 1000000000, param_persistence_threshold: int = 100000,
+                 model_persistence_threshold: int = 2 ** 62, dp_process_group=None, reduce_scatter: bool = True,
+                 overlap_comm: bool = False, offload_optimizer_config=None, offload_param_config=None,
+                 sub_group_size: int = 1000000000000, offload_ratio: float = 0.0, mpu=None, clip_grad: float = 0.0,
+                 gradient_accumulation_dtype=torch.float32, communication_data_type=torch.float16,
+                 postscale_gradients: bool = True, gradient_predivide_factor: float = 1.0,
+                 gradient_accumulation_steps: int = 1, elastic_checkpoint: bool = False, aio_config=None,
+                 all2all_process_group=None, zero_hpz_partition_size: int = 1, zero_quantized_weights: bool = False,
+                 zero_quantized_nontrainable_weights: bool = False, zero_module_granularity_threshold: int = 0,
+                 zeropp_loco_param=None, log_trace_cache_warnings=False, **unused):
+        self.module = module
+        self.optimizer = init_optimizer
+        self.param_names = param_names or {}
+        self.dp_process_group = dp_process_group
+        self.partition_count = dist.get_world_size(group=dp_process_group) if dist.is_initialized() else 1
+        self.rank = dist.get_rank(group=dp_process_group) if dist.is_initialized() else 0
+        self.mpu = mpu
+        self.clip_grad = clip_grad
+        self.gradient_predivide_factor = gradient_predivide_factor
+        self.gradient_accumulation_dtype = gradient_accumulation_dtype or torch.float32
+        self.overflow = False
+        self.skipped_steps = 0
+        self._global_grad_norm = 0.0
+        self.custom_loss_scaler = False
+        self.external_loss_scale = None
+        off = offload_optimizer_config
+        self.offload_optimizer = bool(off is not None and str(getattr(off, "device", "none")).split(".")[-1] == "cpu")
+        dtype = next((p.dtype for p in module.parameters()), torch.float32)
+        self.parameter_offload = DeepSpeedZeRoOffload(module, dp_process_group=dp_process_group,
+                                                      param_persistence_threshold=param_persistence_threshold,
+                                                      offload_param_config=offload_param_config, mpu=mpu, dtype=None)
+        self.parameter_offload.reduce_fn = self._reduce_ready_grads
+        self.dtype = dtype
+        self.loss_scaler = CreateLossScaler(dtype=dtype, static_loss_scale=static_loss_scale,
+                                            dynamic_scaling=dynamic_loss_scale, dynamic_loss_args=dynamic_loss_args)
+        self.dynamic_loss_scale = self.loss_scaler.dynamic
+
+        # fp32 master slices, one flat buffer per param group
+        self.fp16_groups: List[List[torch.nn.Parameter]] = []
+        self.fp32_partitioned_groups_flat: List[torch.Tensor] = []
+        self.grad_partitions = {}
+        for group in self.optimizer.param_groups:
+            params = [p for p in group["params"] if p.requires_grad]
+            self.fp16_groups.append(params)
+            if not params:
+                self.fp32_partitioned_groups_flat.append(torch.empty(0, requires_grad=True))
+                group["params"] = []
+                continue
+            dev = torch.device("cpu") if self.offload_optimizer else params[0].ds_device
+            master = torch.cat([p.ds_tensor.detach().float().view(-1).to(dev) for p in params])
+            master.requires_grad = True
+            self.fp32_partitioned_groups_flat.append(master)
+            group["params"] = [master]
+        if verbose and self.rank == 0:
+            n = sum(p.ds_numel for g in self.fp16_groups for p in g)
+            logger.info(f"ZeRO stage 3: {n} parameters over {self.partition_count} ranks, optimizer offload="
+                        f"{self.offload_optimizer}")
+
+    # ---------------------------------------------------------------------------------------------
+    @property
+    def param_groups(self):
+        return self.optimizer.param_groups
+
+    @property
+    def state(self):
+        return self.optimizer.state
+
+    @property
+    def loss_scale(self):
+        return self.external_loss_scale if self.custom_loss_scaler else self.loss_scaler.cur_scale
+
+    cur_scale = loss_scale
+
+    def zero_grad(self, set_to_none=True):
+        for g in self.fp16_groups:
+            for p in g:
+                p.grad = None
+
+    @torch.no_grad()
+    def _reduce_ready_grads(self, params):
+        """Average ``p.grad`` over the group, keep this rank's slice in the fp32 accumulator, drop the full gradient."""
+        ws = self.partition_count
+        for p in params:
+            if p.grad is None:
+                continue
+            psize = p.ds_partition_numel
+            g = p.grad.detach().reshape(-1)
+            buf = torch.zeros(psize * ws, dtype=g.dtype, device=g.device)
+            buf[:g.numel()].copy_(g)
+            if ws > 1:
+                if self.gradient_predivide_factor != 1.0:
+                    buf.div_(self.gradient_predivide_factor)
+                out = torch.empty(psize, dtype=buf.dtype, device=buf.device)
+                dist.reduce_scatter_tensor(out, buf, group=self.dp_process_group)
+                out.div_(ws / self.gradient_predivide_factor)
+            else:
+                out = buf
+            out = out.to(self.gradient_accumulation_dtype)
+            if p.ds_id in self.grad_partitions:
+                self.grad_partitions[p.ds_id].add_(out)
+            else:
+                self.grad_partitions[p.ds_id] = out.clone()
+            p.grad = None
+
+    def backward(self, loss, retain_graph: bool = False):
+        if self.custom_loss_scaler:
+            (loss * self.external_loss_scale).backward(retain_graph=retain_graph)
+        else:
+            self.loss_scaler.backward(loss.float(), retain_graph=retain_graph)
+        # sweep: gradients that materialised after their module's hook, and parameters still gathered
+        self._reduce_ready_grads([p for g in self.fp16_groups for p in g if p.grad is not None])
+        for g in self.fp16_groups:
+            for p in g:
+                if p.ds_status == ZeroParamStatus.AVAILABLE and not p.ds_persist:
+                    p.ds_active_sub_modules.clear()
+                    _partition_param(p)
+
+    def _all_reduce_scalar(self, v: float, op) -> float:
+        if self.partition_count == 1 and self.mpu is None:
+            return v
+        dev = next((p.ds_device for g in self.fp16_groups for p in g), torch.device("cpu"))
+        t = torch.tensor([float(v)], dtype=torch.float32, device=dev)
+        if self.partition_count > 1:
+            dist.all_reduce(t, op=op, group=self.dp_process_group)
+        if self.mpu is not None:
+            dist.all_reduce(t, op=op, group=self.mpu.get_model_parallel_group())
+        return float(t[0])
+
+    def get_global_grad_norm(self):
+        return self._global_grad_norm
+
+    @torch.no_grad()
+    def step(self, closure=None):
+        local_bad = 0.0
+        sq = 0.0
+        for g in self.grad_partitions.values():
+            s = float(g.float().sum())
+            if s in (float("inf"), -float("inf")) or s != s:
+                local_bad = 1.0
+            sq += float(g.float().norm(2)) ** 2
+        self.overflow = self._all_reduce_scalar(local_bad, dist.ReduceOp.MAX) > 0
+        prev = self.loss_scale
+        if not self.custom_loss_scaler:
+            self.loss_scaler.update_scale(self.overflow)
+        if self.overflow:
+            self.skipped_steps += 1
+            self.grad_partitions = {}
+            if self.rank == 0:
+                logger.info(f"[deepspeed] OVERFLOW! Skipping step. Attempted loss scale: {prev}, reducing to {self.loss_scale}")
+            return
+        scaled_norm = math.sqrt(self._all_reduce_scalar(sq, dist.ReduceOp.SUM))
+        self._global_grad_norm = scaled_norm / prev
+        combined = prev
+        if self.clip_grad > 0.0:
+            clip = (scaled_norm / prev + 1e-6) / self.clip_grad
+            if clip > 1:
+                combined = clip * prev
+        for gi, params in enumerate(self.fp16_groups):
+            master = self.fp32_partitioned_groups_flat[gi]
+            if not params:
+                continue
+            grads = []
+            for p in params:
+                g = self.grad_partitions.get(p.ds_id)
+                grads.append(g.float().to(master.device) if g is not None else
+                             torch.zeros(p.ds_partition_numel, dtype=torch.float32, device=master.device))
+            master.grad = torch.cat(grads).div_(combined)
+        self.grad_partitions = {}
+        self.optimizer.step()
+        for gi, params in enumerate(self.fp16_groups):
+            master = self.fp32_partitioned_groups_flat[gi]
+            master.grad = None
+            off = 0
+            for p in params:
+                n = p.ds_partition_numel
+                p.ds_tensor.copy_(master.detach().narrow(0, off, n).to(p.ds_tensor.dtype))
+                off += n
+                if p.ds_status == ZeroParamStatus.AVAILABLE:  # persistent parameters: refresh the resident full copy
+                    p.ds_status = ZeroParamStatus.NOT_AVAILABLE
+                    all_gather_params([p])
+
+    # ---------------------------------------------------------------------------------------------
+    def state_dict(self):
+        return {"loss_scaler": self.loss_scaler, "dynamic_loss_scale": self.dynamic_loss_scale, "overflow": self.overflow,
+                "partition_count": self.partition_count, "zero_stage": 3,
+                "optimizer_state_dict": self.optimizer.state_dict(),
+                "fp32_flat_groups": [m.detach().clone() for m in self.fp32_partitioned_groups_flat],
+                "param_shapes": [{self.param_names.get(p, f"group{gi}_param{i}"): tuple(p.ds_shape)
+                                  for i, p in enumerate(params)} for gi, params in enumerate(self.fp16_groups)]}
+
+    def load_state_dict(self, state_dict_list, load_optimizer_states=True, load_from_fp32_weights=False,
+                        checkpoint_folder=None, load_serial=None, param_shapes=None):
+        sd = state_dict_list[self.rank] if isinstance(state_dict_list, (list, tuple)) else state_dict_list
+        if sd.get("partition_count", self.partition_count) != self.partition_count:
+            raise RuntimeError("ZeRO-3 checkpoints can only be loaded with the data-parallel size they were saved with")
+        self.loss_scaler = sd.get("loss_scaler", self.loss_scaler)
+        self.overflow = sd.get("overflow", False)
+        if load_optimizer_states:
+            self.optimizer.load_state_dict(sd["optimizer_state_dict"])
+        for cur, saved in zip(self.fp32_partitioned_groups_flat, sd["fp32_flat_groups"]):
+            cur.data.copy_(saved.data.to(cur.device))
+        for gi, params in enumerate(self.fp16_groups):
+            master, off = self.fp32_partitioned_groups_flat[gi], 0
+            for p in params:
+                n = p.ds_partition_numel
+                p.ds_tensor.copy_(master.detach().narrow(0, off, n).to(p.ds_tensor.dtype))
+                off += n
+                if p.ds_status == ZeroParamStatus.AVAILABLE:
+                    p.ds_status = ZeroParamStatus.NOT_AVAILABLE
+                    all_gather_params([p])
+
+    def get_fp32_state_dict_on_rank0(self):
+        """Gather full fp32 parameters (for ``save_16bit_model`` / consolidation)."""
+        out = {}
+        for gi, params in enumerate(self.fp16_groups):
+            master, off = self.fp32_partitioned_groups_flat[gi], 0
+            for i, p in enumerate(params):
+                n = p.ds_partition_numel
+                local = master.detach().narrow(0, off, n).to(p.ds_device)
+                off += n
+                if self.partition_count > 1:
+                    full = torch.empty(n * self.partition_count, dtype=local.dtype, device=local.device)
+                    dist.all_gather_into_tensor(full, local.contiguous(), group=self.dp_process_group)
+                else:
+                    full = local
+                out[self.param_names.get(p, f"group{gi}_param{i}")] = full[:p.ds_numel].view(p.ds_shape).cpu()
+        return out
+
+
+def estimate_zero3_model_states_mem_needs(total_params, largest_layer_params, num_gpus_per_node=1, num_nodes=1,
+                                          cpu_offload=True, cpu_offload_params=True, zero_init=True,
+                                          additional_buffer_factor=1.5):
+    """(cpu bytes, gpu bytes, largest-layer bytes) — reference ``stage3.py:3044``."""
+    total_gpus = num_nodes * num_gpus_per_node
+    gpus_factor = 1 / num_nodes
+    largest_layer_memory = 4 * largest_layer_params
+    if cpu_offload:
+        if cpu_offload_params:
+            gpu_mem = largest_layer_memory
+            cpu_mem = total_params * (18 * gpus_factor if zero_init else max(4 * num_gpus_per_node, 18 * gpus_factor)) * additional_buffer_factor
+        else:
+            gpu_mem = largest_layer_memory + int(2 * total_params / total_gpus)
+            cpu_mem = total_params * (16 * gpus_factor if zero_init else max(4 * num_gpus_per_node, 16 * gpus_factor)) * additional_buffer_factor
+    else:
+        gpu_mem = largest_layer_memory + int(18 * total_params / total_gpus)
+        cpu_mem = largest_layer_params * 4 * num_gpus_per_node * additional_buffer_factor if zero_init else \
+            total_params * 4 * num_gpus_per_node * additional_buffer_factor
+    return int(cpu_mem), int(gpu_mem), largest_layer_memory

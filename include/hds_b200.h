@@ -193,6 +193,20 @@ int hds_paged_attention_prefill(const void* q, void* out, const void* kv_cache_l
 /* Scratch bytes for n_splits > 1 (0 when n_splits <= 1). Zero it once; the kernel leaves its tickets zeroed. */
 int64_t hds_paged_attention_prefill_workspace_bytes(int n_items, int n_q_heads, int head_dim, int n_splits);
 
+/* ---- fused multi-tensor optimizers (training runtime) ----------------------------------------------- */
+/* One Adam / AdamW (adamw_mode = 1: decoupled decay) or Lion step over n_tensors tensors. params / grads / exp_avg /
+ * exp_avg_sq / numels are HOST arrays of device pointers and element counts. dtype codes: 0 bf16, 1 fp16, 2 fp32;
+ * supported (param, grad) pairs: (2,2) (2,0) (2,1) (0,0) (1,1) (0,2) (1,2); moments are fp32. grads are multiplied by
+ * grad_scale first (1 / loss scale, or a clipping coefficient). step counts from 1.
+ * Ref: csrc/adam/multi_tensor_adam.cu, csrc/lion/multi_tensor_lion.cu. */
+int hds_multi_tensor_adam(int n_tensors, void* const* params, const void* const* grads, float* const* exp_avg,
+                          float* const* exp_avg_sq, const int64_t* numels, int param_dtype, int grad_dtype, float lr,
+                          float beta1, float beta2, float eps, float weight_decay, int step, int adamw_mode,
+                          int bias_correction, float grad_scale, void* stream);
+int hds_multi_tensor_lion(int n_tensors, void* const* params, const void* const* grads, float* const* exp_avg,
+                          const int64_t* numels, int param_dtype, int grad_dtype, float lr, float beta1, float beta2,
+                          float weight_decay, float grad_scale, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

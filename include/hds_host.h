@@ -72,6 +72,18 @@ int32_t hds_aio_pending(void* h);
 int hds_mem_lock(void* ptr, int64_t nbytes);
 int hds_mem_unlock(void* ptr, int64_t nbytes);
 
+/* ---- host optimizers (ZeRO-Offload) ---------------------------------------------------------------- */
+/* One step over n fp32 elements in host memory. copy_out (may be NULL) receives the updated parameters converted
+ * to copy_dtype (0 bf16, 1 fp16, 2 fp32) in the same pass. threads <= 0: hardware concurrency. step counts from 1.
+ * Ref: csrc/adam/cpu_adam_impl.cpp, csrc/adagrad/cpu_adagrad.cpp, csrc/lion/cpu_lion_impl.cpp. Returns 0 / -1. */
+int hds_cpu_adam_step(float* params, const float* grads, float* exp_avg, float* exp_avg_sq, int64_t n, float lr,
+                      float beta1, float beta2, float eps, float weight_decay, int step, int adamw_mode,
+                      int bias_correction, void* copy_out, int copy_dtype, int threads);
+int hds_cpu_adagrad_step(float* params, const float* grads, float* exp_avg_sq, int64_t n, float lr, float eps,
+                         float weight_decay, void* copy_out, int copy_dtype, int threads);
+int hds_cpu_lion_step(float* params, const float* grads, float* exp_avg, int64_t n, float lr, float beta1, float beta2,
+                      float weight_decay, void* copy_out, int copy_dtype, int threads);
+
 #ifdef __cplusplus
 }
 #endif

@@ -1,0 +1,164 @@
+"""Worker functions for the multi-rank training-runtime tests (must be importable by spawned processes)."""
+import os
+
+import torch
+
+
+class TinyNet(torch.nn.Module):
+    def __init__(self, hidden=32, nlayers=3):
+        super().__init__()
+        self.layers = torch.nn.ModuleList([torch.nn.Linear(hidden, hidden) for _ in range(nlayers)])
+        self.head = torch.nn.Linear(hidden, 1)
+
+    def forward(self, x, y):
+        for l in self.layers:
+            x = torch.tanh(l(x))
+        return torch.nn.functional.mse_loss(self.head(x).squeeze(-1), y)
+
+
+def make_batches(n, bs, hidden=32, seed=0):
+    g = torch.Generator().manual_seed(seed)
+    return [(torch.randn(bs, hidden, generator=g), torch.randn(bs, generator=g)) for _ in range(n)]
+
+
+def reference_run(steps, global_bs, lr=1e-2, hidden=32, clip=0.0, wd=0.0):
+    """Single-process fp32 AdamW on the full global batch — what every parallel configuration must reproduce."""
+    torch.manual_seed(1234)
+    m = TinyNet(hidden)
+    opt = torch.optim.AdamW(m.parameters(), lr=lr, weight_decay=wd)
+    losses = []
+    for x, y in make_batches(steps, global_bs, hidden):
+        loss = m(x, y)
+        loss.backward()
+        if clip > 0:
+            torch.nn.utils.clip_grad_norm_(m.parameters(), clip)
+        opt.step()
+        opt.zero_grad()
+        losses.append(float(loss))
+    return losses, {k: v.clone() for k, v in m.state_dict().items()}
+
+
+def zero_worker(rank, world, stage, steps, gas, offload, dtype_name, ckpt_dir):
+    import hcache_deepspeed_b200 as ds
+    ds.init_distributed(dist_backend="gloo")
+    torch.manual_seed(1234)
+    hidden, micro = 32, 4
+    model = TinyNet(hidden)
+    cfg = {"train_micro_batch_size_per_gpu": micro, "gradient_accumulation_steps": gas,
+           "optimizer": {"type": "AdamW", "params": {"lr": 1e-2, "weight_decay": 0.0}},
+           "zero_optimization": {"stage": stage, "stage3_param_persistence_threshold": 0}, "steps_per_print": 1000}
+    if offload:
+        cfg["zero_optimization"]["offload_optimizer"] = {"device": "cpu"}
+    if dtype_name == "bf16":
+        cfg["bf16"] = {"enabled": True}
+    elif dtype_name == "fp16":
+        cfg["fp16"] = {"enabled": True, "initial_scale_power": 8}
+    engine, opt, _, _ = ds.initialize(model=model, config=cfg)
+    global_bs = micro * gas * world
+    losses = []
+    for step, (x, y) in enumerate(make_batches(steps, global_bs, hidden)):
+        step_loss = 0.0
+        for a in range(gas):
+            lo = (a * world + rank) * micro
+            xb, yb = x[lo:lo + micro], y[lo:lo + micro]
+            if dtype_name != "fp32":
+                xb = xb.to(torch.bfloat16 if dtype_name == "bf16" else torch.float16)
+                yb = yb.to(xb.dtype)
+            loss = engine(xb, yb)
+            engine.backward(loss)
+            engine.step()
+            step_loss += float(loss) / gas
+        losses.append(step_loss)
+        if ckpt_dir and step == steps // 2 - 1:
+            engine.save_checkpoint(ckpt_dir, tag="mid", client_state={"note": 7})
+    out = {"losses": losses, "global_steps": engine.global_steps}
+    if stage == 3:
+        from hcache_deepspeed_b200.runtime.zero import GatheredParameters
+        sd = {}
+        for n, p in engine.module.named_parameters():
+            with GatheredParameters([p]):
+                sd[n] = p.data.detach().float().clone()
+        out["state"] = sd
+    else:
+        out["state"] = {k: v.detach().float().clone() for k, v in engine.module.state_dict().items()}
+    if ckpt_dir:
+        # resume from the mid-run checkpoint in a fresh engine and replay the second half
+        torch.manual_seed(99)
+        model2 = TinyNet(hidden)
+        engine2, _, _, _ = ds.initialize(model=model2, config=cfg)
+        path, client = engine2.load_checkpoint(ckpt_dir, tag="mid")
+        assert path is not None and client["note"] == 7 and engine2.global_steps == steps // 2
+        relosses = []
+        for step, (x, y) in enumerate(make_batches(steps, global_bs, hidden)):
+            if step < steps // 2:
+                continue
+            sl = 0.0
+            for a in range(gas):
+                lo = (a * world + rank) * micro
+                loss = engine2(x[lo:lo + micro], y[lo:lo + micro])
+                engine2.backward(loss)
+                engine2.step()
+                sl += float(loss) / gas
+            relosses.append(sl)
+        out["resumed_losses"] = relosses
+    return out
+
+
+class _Stage(torch.nn.Module):
+    def __init__(self, hidden):
+        super().__init__()
+        self.l = torch.nn.Linear(hidden, hidden)
+
+    def forward(self, x):
+        return torch.tanh(self.l(x))
+
+
+def pipe_worker(rank, world, stages, steps, micro_batches):
+    import hcache_deepspeed_b200 as ds
+    from hcache_deepspeed_b200.runtime.pipe import LayerSpec, PipelineModule
+    ds.init_distributed(dist_backend="gloo")
+    hidden, micro = 16, 4
+    torch.manual_seed(7)
+    specs = [LayerSpec(_Stage, hidden) for _ in range(4)] + [LayerSpec(torch.nn.Linear, hidden, 1)]
+    net = PipelineModule(layers=specs, num_stages=stages, loss_fn=lambda out, y: torch.nn.functional.mse_loss(out.squeeze(-1), y),
+                         partition_method="uniform", seed_layers=True, base_seed=100)
+    dp = world // stages
+    cfg = {"train_micro_batch_size_per_gpu": micro, "gradient_accumulation_steps": micro_batches,
+           "optimizer": {"type": "Adam", "params": {"lr": 1e-2, "torch_adam": True}}, "steps_per_print": 1000}
+    engine, _, _, _ = ds.initialize(model=net, config=cfg)
+    dp_rank = engine.grid.get_data_parallel_id()
+    losses = []
+    for step in range(steps):
+        g = torch.Generator().manual_seed(1000 + step)
+        x = torch.randn(micro_batches * dp * micro, hidden, generator=g)
+        y = torch.randn(micro_batches * dp * micro, generator=g)
+        mbs = []
+        for m in range(micro_batches):
+            lo = (m * dp + dp_rank) * micro
+            mbs.append((x[lo:lo + micro], y[lo:lo + micro]))
+        losses.append(float(engine.train_batch(iter(mbs))))
+    ev = float(engine.eval_batch(iter(mbs)))
+    return {"losses": losses, "eval": ev, "stage": engine.stage_id, "parts": list(net.parts)}
+
+
+def pipe_reference(steps, micro_batches, dp):
+    hidden, micro = 16, 4
+    layers = []
+    for i in range(4):
+        torch.manual_seed(100 + i)
+        layers.append(_Stage(hidden))
+    torch.manual_seed(104)
+    layers.append(torch.nn.Linear(hidden, 1))
+    net = torch.nn.Sequential(*layers)
+    opt = torch.optim.Adam(net.parameters(), lr=1e-2)
+    losses = []
+    for step in range(steps):
+        g = torch.Generator().manual_seed(1000 + step)
+        x = torch.randn(micro_batches * dp * micro, hidden, generator=g)
+        y = torch.randn(micro_batches * dp * micro, generator=g)
+        loss = torch.nn.functional.mse_loss(net(x).squeeze(-1), y)
+        loss.backward()
+        opt.step()
+        opt.zero_grad()
+        losses.append(float(loss))
+    return losses

@@ -1,0 +1,235 @@
+"""Training runtime on CPU (gloo): config resolution, LR schedules, loss scaling, optimizers, ZeRO 0/1/2/3 against a
+single-process fp32 reference, checkpoint resume, pipeline parallelism. Mirrors the reference's
+tests/unit/runtime/{test_ds_config_dict,test_lr_schedulers,zero/test_zero,half_precision,pipe}."""
+import math
+
+import pytest
+import torch
+
+from tests.dist_utils import run_distributed
+from tests.runtime_helper import pipe_reference, pipe_worker, reference_run, zero_worker
+
+pytestmark = pytest.mark.timeout(600)
+
+
+def test_batch_size_resolution():
+    from hcache_deepspeed_b200.runtime.config import DeepSpeedConfig, DeepSpeedConfigError
+    c = DeepSpeedConfig({"train_batch_size": 32, "gradient_accumulation_steps": 2}, world_size=4)
+    assert (c.train_batch_size, c.train_micro_batch_size_per_gpu, c.gradient_accumulation_steps) == (32, 4, 2)
+    c = DeepSpeedConfig({"train_micro_batch_size_per_gpu": 3}, world_size=2)
+    assert (c.train_batch_size, c.gradient_accumulation_steps) == (6, 1)
+    c = DeepSpeedConfig({"train_batch_size": 16, "train_micro_batch_size_per_gpu": 2}, world_size=2)
+    assert c.gradient_accumulation_steps == 4
+    with pytest.raises(DeepSpeedConfigError):
+        DeepSpeedConfig({"train_batch_size": 10, "train_micro_batch_size_per_gpu": 3, "gradient_accumulation_steps": 1}, world_size=2)
+    with pytest.raises(DeepSpeedConfigError):
+        DeepSpeedConfig({"steps_per_print": 1}, world_size=1)
+    with pytest.raises(DeepSpeedConfigError):
+        DeepSpeedConfig({"train_batch_size": 4, "fp16": {"enabled": True}, "bf16": {"enabled": True}}, world_size=1)
+    c = DeepSpeedConfig({"train_batch_size": 4, "zero_optimization": {"stage": 3, "stage3_max_live_parameters": 5, "cpu_offload": True}},
+                        world_size=1)
+    assert c.zero_config.max_live_parameters == 5 and c.zero_config.overlap_comm and str(c.zero_config.offload_optimizer.device).endswith("cpu")
+
+
+def test_lr_schedules():
+    from hcache_deepspeed_b200.runtime.lr_schedules import LRRangeTest, OneCycle, WarmupCosineLR, WarmupDecayLR, WarmupLR
+    p = [torch.nn.Parameter(torch.zeros(1))]
+    opt = torch.optim.SGD(p, lr=0.1)
+    s = WarmupLR(opt, warmup_min_lr=0.0, warmup_max_lr=0.1, warmup_num_steps=10, warmup_type="linear")
+    lrs = []
+    for _ in range(15):
+        s.step()
+        lrs.append(opt.param_groups[0]["lr"])
+    assert lrs[0] == 0.0 and abs(lrs[5] - 0.05) < 1e-9 and lrs[10] == pytest.approx(0.1) and lrs[14] == pytest.approx(0.1)
+    opt = torch.optim.SGD(p, lr=0.1)
+    s = WarmupDecayLR(opt, total_num_steps=20, warmup_max_lr=0.1, warmup_num_steps=10, warmup_type="log")
+    lrs = []
+    for _ in range(21):
+        s.step()
+        lrs.append(opt.param_groups[0]["lr"])
+    assert lrs[0] == 0.0 and lrs[9] == pytest.approx(0.1 * math.log(10) / math.log(10)) and lrs[15] == pytest.approx(0.05) and lrs[20] == 0.0
+    opt = torch.optim.SGD(p, lr=0.1)
+    s = LRRangeTest(opt, lr_range_test_min_lr=0.01, lr_range_test_step_size=5, lr_range_test_step_rate=1.0, lr_range_test_staircase=True)
+    lrs = []
+    for _ in range(11):
+        s.step()
+        lrs.append(opt.param_groups[0]["lr"])
+    assert lrs[0] == pytest.approx(0.01) and lrs[4] == pytest.approx(0.02) and lrs[9] == pytest.approx(0.03)
+    opt = torch.optim.SGD(p, lr=0.1, momentum=0.9)
+    s = OneCycle(opt, cycle_min_lr=0.01, cycle_max_lr=0.1, cycle_first_step_size=10, decay_step_size=5, decay_lr_rate=0.5)
+    lrs = []
+    for _ in range(30):
+        s.step()
+        lrs.append(opt.param_groups[0]["lr"])
+    assert max(lrs) == pytest.approx(0.1, rel=1e-6) and lrs.index(max(lrs)) == 9 and lrs[19] == pytest.approx(0.01, abs=1e-9)
+    assert lrs[29] < 0.01
+    opt = torch.optim.SGD(p, lr=0.2)
+    s = WarmupCosineLR(opt, total_num_steps=20, warmup_num_steps=5, warmup_type="linear", cos_min_ratio=0.1)
+    lrs = []
+    for _ in range(21):
+        s.step()
+        lrs.append(opt.param_groups[0]["lr"])
+    assert lrs[0] == 0.0 and max(lrs) <= 0.2 + 1e-9 and lrs[20] == pytest.approx(0.02, rel=1e-6)
+    sd = s.state_dict()
+    s.load_state_dict(sd)
+    assert s.last_batch_iteration == 20
+
+
+def test_dynamic_loss_scaler():
+    from hcache_deepspeed_b200.runtime.fp16.loss_scaler import DynamicLossScaler
+    s = DynamicLossScaler(init_scale=2 ** 8, scale_window=2, delayed_shift=2, min_scale=1)
+    s.update_scale(True)   # first overflow only burns a hysteresis credit
+    assert s.cur_scale == 256
+    s.update_scale(True)
+    assert s.cur_scale == 128
+    s.update_scale(False)
+    s.update_scale(False)
+    assert s.cur_scale == 256
+    s = DynamicLossScaler(init_scale=2, min_scale=1, delayed_shift=1)
+    s.update_scale(True)
+    with pytest.raises(Exception):
+        s.update_scale(True)
+
+
+def test_cpu_optimizers_match_torch():
+    from hcache_deepspeed_b200.ops.adam import DeepSpeedCPUAdam, FusedAdam
+    from hcache_deepspeed_b200.ops.adagrad import DeepSpeedCPUAdagrad
+    from hcache_deepspeed_b200.ops.lamb import FusedLamb
+    from hcache_deepspeed_b200.ops.lion import DeepSpeedCPULion, FusedLion
+    torch.manual_seed(0)
+
+    def run(a_cls, b_cls, akw, bkw, n=70001, steps=4):
+        w0 = torch.randn(n)
+        a, b = torch.nn.Parameter(w0.clone()), torch.nn.Parameter(w0.clone())
+        oa, ob = a_cls([a], **akw), b_cls([b], **bkw)
+        for _ in range(steps):
+            g = torch.randn(n)
+            a.grad, b.grad = g.clone(), g.clone()
+            oa.step()
+            ob.step()
+        return float((a - b).abs().max())
+
+    assert run(DeepSpeedCPUAdam, torch.optim.AdamW, dict(lr=1e-2, weight_decay=0.1), dict(lr=1e-2, weight_decay=0.1)) < 1e-5
+    assert run(DeepSpeedCPUAdam, torch.optim.Adam, dict(lr=1e-2, weight_decay=0.1, adamw_mode=False), dict(lr=1e-2, weight_decay=0.1)) < 1e-5
+    assert run(FusedAdam, torch.optim.AdamW, dict(lr=1e-2, weight_decay=0.1), dict(lr=1e-2, weight_decay=0.1)) < 1e-5
+    assert run(DeepSpeedCPUAdagrad, torch.optim.Adagrad, dict(lr=1e-2), dict(lr=1e-2, eps=1e-10)) < 1e-6
+    assert run(DeepSpeedCPULion, FusedLion, dict(lr=1e-3, weight_decay=0.1), dict(lr=1e-3, weight_decay=0.1)) < 1e-5
+    p = torch.nn.Parameter(torch.randn(1000))
+    sh = torch.zeros(1000, dtype=torch.bfloat16)
+    o = DeepSpeedCPUAdam([p], lr=1e-2)
+    p.grad = torch.randn(1000)
+    o.step(fp16_param_groups=[[sh]])
+    assert torch.equal(sh, p.data.to(torch.bfloat16))
+    w = torch.nn.Parameter(torch.randn(50, 20))
+    o = FusedLamb([w], lr=1e-2, weight_decay=0.01)
+    w.grad = torch.randn(50, 20)
+    before = w.detach().clone()
+    o.step()
+    assert 0.01 <= o.get_lamb_coeffs()[0] <= 10 and not torch.equal(before, w.detach())
+
+
+def test_partition_helpers():
+    from hcache_deepspeed_b200.runtime.utils import partition_balanced, partition_uniform
+    assert partition_uniform(10, 3) == [0, 4, 7, 10]
+    assert partition_uniform(2, 4) == [0, 1, 2, 2, 2]
+    parts = partition_balanced([1, 1, 1, 1, 10, 1, 1, 1], 3)
+    w = [1, 1, 1, 1, 10, 1, 1, 1]
+    assert parts[0] == 0 and parts[-1] == 8 and max(sum(w[parts[i]:parts[i + 1]]) for i in range(3)) == 10
+
+
+def test_zero_init_and_gathered_parameters():
+    from hcache_deepspeed_b200.runtime.zero import GatheredParameters, Init, ZeroParamStatus
+    with Init():
+        m = torch.nn.Sequential(torch.nn.Linear(8, 16), torch.nn.ReLU(), torch.nn.Linear(16, 4))
+    p = m[0].weight
+    assert p.ds_status == ZeroParamStatus.NOT_AVAILABLE and p.numel() == 0 and tuple(p.ds_shape) == (16, 8)
+    assert float(p.ds_tensor.abs().sum()) > 0  # initialisers ran on the full tensor before partitioning
+    with GatheredParameters(m.parameters(), modifier_rank=0):
+        assert tuple(m[0].weight.shape) == (16, 8)
+        m[0].weight.data.fill_(1.0)
+    assert p.ds_status == ZeroParamStatus.NOT_AVAILABLE and float(p.ds_tensor.min()) == 1.0
+    assert tuple(torch.nn.Linear(2, 2).weight.shape) == (2, 2)  # constructors restored outside the context
+
+
+def test_activation_checkpointing_matches_plain():
+    from hcache_deepspeed_b200.runtime.activation_checkpointing import checkpointing
+    checkpointing.configure(None, checkpoint_in_cpu=True)
+    torch.manual_seed(0)
+    net = torch.nn.Sequential(torch.nn.Linear(8, 8), torch.nn.Dropout(0.5), torch.nn.Tanh(), torch.nn.Linear(8, 8))
+    x = torch.randn(4, 8, requires_grad=True)
+    torch.manual_seed(5)
+    y = net(x).sum()
+    y.backward()
+    g_plain, gx_plain = [p.grad.clone() for p in net.parameters()], x.grad.clone()
+    for p in net.parameters():
+        p.grad = None
+    x.grad = None
+    torch.manual_seed(5)
+    y2 = checkpointing.checkpoint(net, x).sum()
+    y2.backward()
+    assert torch.allclose(y, y2)
+    for a, p in zip(g_plain, net.parameters()):
+        assert torch.allclose(a, p.grad, atol=1e-6)
+    assert torch.allclose(gx_plain, x.grad, atol=1e-6)
+    checkpointing.configure(None)
+
+
+def test_engine_single_process_fp32_matches_torch():
+    import hcache_deepspeed_b200 as ds
+    from tests.runtime_helper import TinyNet, make_batches
+    want, _ = reference_run(steps=5, global_bs=8, clip=0.5)
+    torch.manual_seed(1234)
+    engine, _, _, sched = ds.initialize(model=TinyNet(), config={
+        "train_batch_size": 8, "gradient_accumulation_steps": 2, "gradient_clipping": 0.5,
+        "optimizer": {"type": "AdamW", "params": {"lr": 1e-2, "weight_decay": 0.0}},
+        "scheduler": {"type": "WarmupLR", "params": {"warmup_min_lr": 1e-2, "warmup_max_lr": 1e-2, "warmup_num_steps": 2}}})
+    got = []
+    for x, y in make_batches(5, 8):
+        tot = 0.0
+        for a in range(2):
+            loss = engine(x[a * 4:(a + 1) * 4], y[a * 4:(a + 1) * 4])
+            engine.backward(loss)
+            engine.step()
+            tot += float(loss) / 2
+        got.append(tot)
+    assert engine.global_steps == 5 and sched is not None and engine.get_global_grad_norm() > 0
+    assert got == pytest.approx(want, rel=2e-4, abs=2e-5)
+
+
+@pytest.mark.parametrize("stage,gas,offload", [(0, 1, False), (1, 2, False), (2, 2, False), (2, 1, True), (3, 2, False), (3, 1, True)])
+def test_zero_stages_match_reference_2ranks(stage, gas, offload, tmp_path):
+    steps, world = 6, 2
+    want, want_state = reference_run(steps=steps, global_bs=4 * gas * world)
+    ckpt = str(tmp_path / "ckpt") if stage in (1, 2, 3) and not offload else None
+    res = run_distributed(zero_worker, world, stage, steps, gas, offload, "fp32", ckpt)
+    for r in res:
+        assert r["global_steps"] == steps
+        for k, v in want_state.items():
+            torch.testing.assert_close(r["state"][k], v, rtol=2e-4, atol=2e-5)
+        if ckpt:
+            # the resumed run's losses equal the uninterrupted run's second half (per rank, local micro-batches)
+            assert r["resumed_losses"] == pytest.approx(r["losses"][steps // 2:], rel=1e-4, abs=1e-5)
+    mean = [sum(r["losses"][i] for r in res) / world for i in range(steps)]
+    assert mean == pytest.approx(want, rel=5e-4, abs=5e-5)
+
+
+@pytest.mark.parametrize("stage,dtype", [(0, "bf16"), (2, "bf16"), (2, "fp16"), (0, "fp16")])
+def test_mixed_precision_trains(stage, dtype):
+    res = run_distributed(zero_worker, 2, stage, 12, 1, False, dtype, None)
+    for r in res:
+        assert all(math.isfinite(l) for l in r["losses"])
+    mean = [sum(r["losses"][i] for r in res) / 2 for i in range(12)]
+    assert sum(mean[-3:]) < sum(mean[:3])  # it learns
+    for k in res[0]["state"]:
+        torch.testing.assert_close(res[0]["state"][k], res[1]["state"][k], rtol=0, atol=0)  # replicas stay in sync
+
+
+@pytest.mark.parametrize("world,stages", [(2, 2), (4, 2)])
+def test_pipeline_matches_sequential(world, stages):
+    steps, mbs = 4, 4
+    want = pipe_reference(steps, mbs, world // stages)
+    res = run_distributed(pipe_worker, world, stages, steps, mbs)
+    for r in res:
+        assert r["losses"] == pytest.approx(want, rel=1e-3, abs=1e-4)
+        assert r["parts"][0] == 0 and r["parts"][-1] == 5 and math.isfinite(r["eval"])
+    assert {r["stage"] for r in res} == set(range(stages))
