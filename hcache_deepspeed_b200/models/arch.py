@@ -261,6 +261,9 @@ def named_arch(name: str) -> ArchSpec:
         "opt-30b": ArchSpec(n_layers=48, hidden=7168, n_heads=56, n_kv_heads=56, head_dim=128, intermediate=28672, **opt),
         "tiny-llama-test": ArchSpec(n_layers=2, hidden=256, n_heads=4, n_kv_heads=2, intermediate=512,
                                     **{**llama, "vocab": 512, "head_dim": 64}),
+        "tiny-mixtral-test": ArchSpec(n_layers=2, hidden=256, n_heads=4, n_kv_heads=2, intermediate=512,
+                                      **{**llama, "vocab": 512, "head_dim": 64, "model_type": "mixtral"}, n_experts=8,
+                                      top_k=2, moe_intermediate=384, norm_topk_prob=True),
         "tiny-opt-test": ArchSpec(n_layers=2, hidden=256, n_heads=4, n_kv_heads=4, intermediate=512,
                                   **{**opt, "vocab": 512, "head_dim": 64, "max_positions": 512}),
     }

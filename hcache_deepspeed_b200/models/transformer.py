@@ -293,32 +293,72 @@ class RaggedTransformer:
         self.ops.gemm(x, lw.w_up, act, bias=lw.b_up, act=self.act, gated=s.gated_mlp, workspace=self.ws_gemm)
         return self._row_parallel(act, lw.w_down, lw.b_down, T, force_accum)
 
+    def _moe_state(self, lw, E: int, kk: int) -> dict:
+        """Persistent routing buffers (shared by all layers) + this layer's stacked expert weights."""
+        if getattr(self, "_moe_bufs", None) is None:
+            dev, dt, Tm = self.device, self.dtype, self._state_config.max_ragged_batch_size
+            rows = self.ops.k.moe_padded_rows(Tm, E, kk)
+            inter = lw.experts[0].w_down.shape[1]
+            self._moe_bufs = dict(
+                logits=torch.empty(Tm, E, dtype=dt, device=dev), scores=torch.empty(Tm, kk, dtype=torch.float32, device=dev),
+                expert_ids=torch.empty(Tm, kk, dtype=torch.int32, device=dev),
+                offsets=torch.empty(Tm, kk, dtype=torch.int32, device=dev),
+                mapped_slots=torch.empty(Tm, kk, dtype=torch.int32, device=dev),
+                counts=torch.zeros(E, dtype=torch.int32, device=dev), pad_off=torch.zeros(E + 1, dtype=torch.int32, device=dev),
+                xs=torch.zeros(rows, self.spec.hidden, dtype=dt, device=dev), hs=torch.zeros(rows, inter, dtype=dt, device=dev),
+                ys=torch.zeros(rows, self.spec.hidden, dtype=dt, device=dev))
+        stacked = self.__dict__.setdefault("_moe_stacked", {})
+        if id(lw) not in stacked:
+            # stack the experts once; the per-expert tensors become views of the stacked storage
+            up = torch.cat([e.w_up for e in lw.experts], dim=0).contiguous()
+            down = torch.cat([e.w_down for e in lw.experts], dim=0).contiguous()
+            nu, nd = lw.experts[0].w_up.shape[0], lw.experts[0].w_down.shape[0]
+            for i, e in enumerate(lw.experts):
+                e.w_up, e.w_down = up[i * nu:(i + 1) * nu], down[i * nd:(i + 1) * nd]
+            stacked[id(lw)] = (up, down)
+        return dict(self._moe_bufs, w_up=stacked[id(lw)][0], w_down=stacked[id(lw)][1])
+
     def _moe(self, x: torch.Tensor, lw, T: int) -> torch.Tensor:
         """Top-k mixture of experts (tensor-parallel experts, no expert parallelism — as the reference's v2:
-        ``inference_transformer_base.py:588``). Routing runs on the small [T, E] score matrix; expert GEMMs
-        accumulate straight into the fp32 pending delta scaled by their gate weight.
-        Ref: modules/implementations/moe/cutlass_multi_gemm.py:28-249, ragged_ops/top_k_gating."""
+        ``inference_transformer_base.py:588``). On the GPU: gate GEMM -> top-k gating kernel -> scatter -> ONE grouped
+        tcgen05 GEMM for all experts' MLP-1 (gated activation in the epilogue) -> ONE grouped GEMM for MLP-2 -> weighted
+        gather straight into the fp32 pending delta; nothing is read back to the host.
+        Ref: modules/implementations/moe/cutlass_multi_gemm.py:28-249, ragged_ops/{top_k_gating,moe_scatter,moe_gather}."""
         s = self.spec
         d32 = self._delta_bufs[self._delta_idx][:T]
-        scores = ref.gemm(x, lw.w_router, out_dtype=torch.float32) if self.device.type == "cpu" else \
-            self.ops.k.gemm(x, lw.w_router).float()
-        probs = torch.softmax(scores, dim=-1)
-        topv, topi = torch.topk(probs, s.top_k, dim=-1)
-        if s.norm_topk_prob:
-            topv = topv / topv.sum(-1, keepdim=True)
         mult = 2 if s.gated_mlp else 1
-        for e, ew in enumerate(lw.experts):
-            sel = (topi == e)
-            rows = sel.any(-1).nonzero(as_tuple=False).flatten()
-            if rows.numel() == 0:
-                continue
-            gate_w = (topv * sel).sum(-1)[rows]
-            xe = x.index_select(0, rows)
-            he = torch.empty((rows.numel(), ew.w_up.shape[0] // mult), dtype=x.dtype, device=x.device)
-            self.ops.gemm(xe, ew.w_up, he, act=self.act, gated=s.gated_mlp)
-            ye = torch.empty((rows.numel(), s.hidden), dtype=x.dtype, device=x.device)
-            self.ops.gemm(he, ew.w_down, ye)
-            d32.index_add_(0, rows, ye.float() * gate_w[:, None])
+        if self.device.type == "cuda":
+            k = self.ops.k
+            E, kk = len(lw.experts), s.top_k
+            st = self._moe_state(lw, E, kk)
+            logits = k.gemm(x, lw.w_router, out=st["logits"][:T])
+            k.moe_topk_gating(logits, kk, s.norm_topk_prob, st["scores"][:T], st["expert_ids"][:T], st["offsets"][:T],
+                              st["counts"])
+            rows = k.moe_padded_rows(T, E, kk)
+            xs, hs, ys = st["xs"][:rows], st["hs"][:rows], st["ys"][:rows]
+            k.moe_scatter(x, xs, st["expert_ids"][:T], st["offsets"][:T], st["counts"], st["pad_off"],
+                          st["mapped_slots"][:T], kk)
+            k.moe_gemm(xs, st["w_up"], st["pad_off"], E, hs, act=self.act, gated=s.gated_mlp)
+            k.moe_gemm(hs, st["w_down"], st["pad_off"], E, ys)
+            k.moe_gather(ys, st["mapped_slots"][:T], st["scores"][:T], d32)
+        else:
+            scores = ref.gemm(x, lw.w_router, out_dtype=torch.float32)
+            probs = torch.softmax(scores, dim=-1)
+            topv, topi = torch.topk(probs, s.top_k, dim=-1)
+            if s.norm_topk_prob:
+                topv = topv / topv.sum(-1, keepdim=True)
+            for e, ew in enumerate(lw.experts):
+                sel = (topi == e)
+                rows = sel.any(-1).nonzero(as_tuple=False).flatten()
+                if rows.numel() == 0:
+                    continue
+                gate_w = (topv * sel).sum(-1)[rows]
+                xe = x.index_select(0, rows)
+                he = torch.empty((rows.numel(), ew.w_up.shape[0] // mult), dtype=x.dtype, device=x.device)
+                self.ops.gemm(xe, ew.w_up, he, act=self.act, gated=s.gated_mlp)
+                ye = torch.empty((rows.numel(), s.hidden), dtype=x.dtype, device=x.device)
+                self.ops.gemm(he, ew.w_down, ye)
+                d32.index_add_(0, rows, ye.float() * gate_w[:, None])
         if lw.shared_expert is not None:
             se = lw.shared_expert
             hs = torch.empty((T, se.w_up.shape[0] // mult), dtype=x.dtype, device=x.device)

@@ -341,6 +341,44 @@ extern "C" int hds_gemm_accum(const void* A, int64_t lda, const void* W, int64_t
                       : launch_gemm_bn<EPI_RED_F32, false>(bn, ops.ta, ops.tw, g, grid, s);
 }
 
+/* Grouped GEMM over experts: rows [pad_off[e], pad_off[e+1]) of A use W[e*N : (e+1)*N]. */
+extern "C" int hds_moe_gemm(const void* A, int64_t lda, const void* W_stacked, int64_t ldw, const int32_t* pad_off,
+                            int n_experts, int max_rows, int N, int K, int dtype, int epilogue, int act, void* out,
+                            int64_t ldo, void* stream) {
+    HDS_REQUIRE(epilogue == EPI_STORE || epilogue == EPI_GATED, "hds_moe_gemm: epilogue must be 0 (store) or 1 (gated)");
+    HDS_REQUIRE(dtype == 0 || dtype == 1, "hds_moe_gemm: dtype must be 0 (bf16) or 1 (fp16)");
+    HDS_REQUIRE(n_experts >= 1 && pad_off != nullptr && max_rows % kGemmBM == 0,
+                "hds_moe_gemm: needs expert offsets and a row capacity that is a multiple of 128");
+    HDS_REQUIRE(epilogue != EPI_GATED || (N % 2 == 0), "hds_moe_gemm: gated epilogue needs an even N");
+    GemmArgs g;
+    memset(&g, 0, sizeof(g));
+    Operands ops;
+    const int bn = N >= 256 ? 256 : 128;
+    int rc = prepare(g, ops, A, lda, W_stacked, ldw, max_rows, N, K, dtype == 0, bn, 1);
+    if (rc) return rc;
+    // the weight map spans every expert: n_experts * N rows
+    rc = make_tmap_2d_16b(&ops.tw, W_stacked, static_cast<uint64_t>(K), static_cast<uint64_t>(N) * n_experts,
+                          static_cast<uint64_t>(ldw) * 2, kGemmBK, bn, dtype == 0);
+    if (rc) return rc;
+    g.act = act;
+    g.out = out;
+    g.ldo = ldo;
+    g.group_pad_off = pad_off;
+    g.n_groups = n_experts;
+    const int grid = grid_for(g, bn);
+    cudaStream_t s = static_cast<cudaStream_t>(stream);
+    if (dtype == 0) {
+        return epilogue == EPI_STORE ? (bn == 128 ? launch_gemm_inst<128, EPI_STORE, true>(ops.ta, ops.tw, g, grid, s)
+                                                  : launch_gemm_inst<256, EPI_STORE, true>(ops.ta, ops.tw, g, grid, s))
+                                     : (bn == 128 ? launch_gemm_inst<128, EPI_GATED, true>(ops.ta, ops.tw, g, grid, s)
+                                                  : launch_gemm_inst<256, EPI_GATED, true>(ops.ta, ops.tw, g, grid, s));
+    }
+    return epilogue == EPI_STORE ? (bn == 128 ? launch_gemm_inst<128, EPI_STORE, false>(ops.ta, ops.tw, g, grid, s)
+                                              : launch_gemm_inst<256, EPI_STORE, false>(ops.ta, ops.tw, g, grid, s))
+                                 : (bn == 128 ? launch_gemm_inst<128, EPI_GATED, false>(ops.ta, ops.tw, g, grid, s)
+                                              : launch_gemm_inst<256, EPI_GATED, false>(ops.ta, ops.tw, g, grid, s));
+}
+
 static int gemm_rope_common(bool has_q, const void* A, int64_t lda, const void* W, int64_t ldw, int M, int K,
                             int dtype, const void* bias, void* q_out, void* kv_cache_layer, const int32_t* tok_pos,
                             const int32_t* tok_slot, const float* inv_freq, int n_q_heads, int n_kv_heads,

@@ -87,7 +87,25 @@ struct GemmArgs {
     const int32_t* tok_slot;  // [M] block_id * block_size + in-block offset; < 0 = skip token
     const float* inv_freq;    // [rotary_dim / 2]
     int n_q_heads, n_kv_heads, block_size, do_rope;
+    // grouped (mixture-of-experts) mode: A rows [group_pad_off[e], group_pad_off[e+1]) belong to expert e (ranges are
+    // multiples of 128 so no tile straddles two experts); W stacks the experts' [N, K] matrices along its rows.
+    // M is the row capacity of A / out; tiles at or beyond group_pad_off[n_groups] are skipped.
+    const int32_t* group_pad_off;
+    int n_groups;
 };
+
+// Expert that owns the 128-row tile starting at row0 (-1: past the last expert's rows).
+__device__ __forceinline__ int gemm_group_of(const GemmArgs& a, int row0) {
+    const int32_t* off = a.group_pad_off;
+    if (row0 >= off[a.n_groups]) return -1;
+    int lo = 0, hi = a.n_groups;
+    while (hi - lo > 1) {
+        const int mid = (lo + hi) >> 1;
+        if (off[mid] <= row0) lo = mid;
+        else hi = mid;
+    }
+    return lo;
+}
 
 template <bool kBf16>
 __device__ __forceinline__ void store_row32(void* dst, const float (&v)[32]) {
@@ -427,6 +445,12 @@ gemm_tn_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
                 const int sp = rest / n_tiles;
                 const int kb0 = sp * args.kb_per_split;
                 const int kb1 = min(kb_total, kb0 + args.kb_per_split);
+                int w_row0 = n_t * BN;
+                if (args.group_pad_off != nullptr) {
+                    const int e = gemm_group_of(args, m_t * kGemmBM);
+                    if (e < 0) continue;
+                    w_row0 += e * args.N;
+                }
                 // Single m-tile (decode): every CTA needs the SAME activation k-block at the same moment, i.e. 148
                 // requests for a handful of L2 lines per step — the lines' L2 slices serialise them (~0.3 us per
                 // k-block, independent of tile size or pipeline depth). Starting each CTA at a different k offset
@@ -452,7 +476,7 @@ gemm_tn_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
                         tma_load_3d(smem_w + stage * W_BYTES, &tmap_w, &full_bar[stage], 0, kb * 32, n_t * (BN / 32),
                                     m_tiles > 1 ? kEvictNormal : kEvictFirst);
                     else
-                        tma_load_2d(smem_w + stage * W_BYTES, &tmap_w, &full_bar[stage], kb * kGemmBK, n_t * BN,
+                        tma_load_2d(smem_w + stage * W_BYTES, &tmap_w, &full_bar[stage], kb * kGemmBK, w_row0,
                                     m_tiles > 1 ? kEvictNormal : kEvictFirst);
                     if (++stage == STAGES) {
                         stage = 0;
@@ -469,6 +493,7 @@ gemm_tn_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
                 const int sp = (w / m_tiles) / n_tiles;
                 const int kb0 = sp * args.kb_per_split;
                 const int kb1 = min(kb_total, kb0 + args.kb_per_split);
+                if (args.group_pad_off != nullptr && gemm_group_of(args, (w % m_tiles) * kGemmBM) < 0) continue;
                 mbar_wait(&tempty_bar[acc], acc_phase ^ 1);
                 tc_fence_after();
                 const uint32_t d_tmem = tmem_base + acc * BN;
@@ -506,6 +531,7 @@ gemm_tn_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
             const int rest = w / m_tiles;
             const int n_t = rest % n_tiles;
             const int sp = rest / n_tiles;
+            if (args.group_pad_off != nullptr && gemm_group_of(args, m_t * kGemmBM) < 0) continue;
             mbar_wait(&tfull_bar[acc], acc_phase);
             tc_fence_after();
             const uint32_t taddr = tmem_base + ((quad * 32u) << 16) + acc * BN;

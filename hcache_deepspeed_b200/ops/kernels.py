@@ -348,3 +348,59 @@ def paged_attention_prefill(q: torch.Tensor, out: torch.Tensor, kv_cache_layer: 
                                          _dt(q), _stream())
     native.check(rc, "hds_paged_attention_prefill")
     _count()
+
+
+# ------------------------------------------------------------------------------------------------
+# mixture of experts (ref: ragged_ops/top_k_gating, moe_scatter, moe_gather, cutlass_ops/moe_gemm)
+# ------------------------------------------------------------------------------------------------
+def moe_padded_rows(n_tokens: int, n_experts: int, top_k: int) -> int:
+    """Row capacity of the scattered activation buffer (each expert's range is padded to 128 rows)."""
+    return int(native.cuda_lib().hds_moe_padded_rows(n_tokens, n_experts, top_k))
+
+
+def moe_topk_gating(logits: torch.Tensor, top_k: int, normalize: bool, scores: torch.Tensor, expert_ids: torch.Tensor,
+                    offsets: torch.Tensor, counts: torch.Tensor) -> None:
+    """Softmax + top-k per token; ``counts`` (int32 [E], zero on entry) is incremented per assignment."""
+    T, E = logits.shape
+    code = 2 if logits.dtype == torch.float32 else _dt(logits)
+    rc = native.cuda_lib().hds_moe_topk_gating(_p(logits), logits.stride(0), T, E, top_k, int(normalize), code, _p(scores),
+                                               _p(expert_ids), _p(offsets), _p(counts), _stream())
+    native.check(rc, "hds_moe_topk_gating")
+    _count()
+
+
+def moe_scatter(x: torch.Tensor, xs: torch.Tensor, expert_ids: torch.Tensor, offsets: torch.Tensor, counts: torch.Tensor,
+                pad_off: torch.Tensor, mapped_slots: torch.Tensor, top_k: int) -> None:
+    """Build ``pad_off`` (int32 [E+1]) from ``counts`` (re-zeroed) and copy every token row to its k expert rows."""
+    T, H = x.shape
+    E = counts.numel()
+    rc = native.cuda_lib().hds_moe_scatter(_p(x), x.stride(0), _p(xs), xs.stride(0), _p(expert_ids), _p(offsets), _p(counts),
+                                           _p(pad_off), _p(mapped_slots), T, E, top_k, H, _stream())
+    native.check(rc, "hds_moe_scatter")
+    _count(2)
+
+
+def moe_gemm(a: torch.Tensor, w_stacked: torch.Tensor, pad_off: torch.Tensor, n_experts: int, out: torch.Tensor,
+             act: int = ACT_IDENTITY, gated: bool = False) -> torch.Tensor:
+    """Grouped GEMM: rows of ``a`` in expert e's range times ``w_stacked[e*N:(e+1)*N]``ᵀ (``w_stacked``: [E*N, K])."""
+    _check_2d(a, "a")
+    _check_2d(out, "out")
+    rows, K = a.shape
+    N = w_stacked.shape[0] // n_experts
+    assert w_stacked.shape[1] == K and rows % 128 == 0 and out.shape[0] >= rows
+    rc = native.cuda_lib().hds_moe_gemm(_p(a), a.stride(0), _p(w_stacked), w_stacked.stride(0), _p(pad_off), n_experts, rows,
+                                        N, K, _dt(a), EPI_GATED if gated else EPI_STORE, act, _p(out), out.stride(0),
+                                        _stream())
+    native.check(rc, "hds_moe_gemm")
+    _count()
+    return out
+
+
+def moe_gather(y: torch.Tensor, mapped_slots: torch.Tensor, scores: torch.Tensor, out: torch.Tensor) -> None:
+    """``out[t] += sum_j scores[t, j] * y[mapped_slots[t, j]]`` (``out`` fp32)."""
+    T, k = mapped_slots.shape
+    assert out.dtype == torch.float32
+    rc = native.cuda_lib().hds_moe_gather(_p(y), y.stride(0), _p(mapped_slots), _p(scores), _p(out), out.stride(0), T, k,
+                                          y.shape[1], _dt(y), _stream())
+    native.check(rc, "hds_moe_gather")
+    _count()

@@ -51,6 +51,10 @@ def _declare_cuda(lib: ctypes.CDLL) -> None:
         "hds_p2p_gather_rows": [P, P, I, I, I, L, I, P],
         "hds_paged_attention_splitkv": [P, P, P, L, P, I, P, I, I, I, I, I, I, I, F, P, L, I, P],
         "hds_paged_attention_prefill": [P, P, P, L, P, I, P, I, I, I, I, I, I, F, I, P, L, I, P],
+        "hds_moe_topk_gating": [P, L, I, I, I, I, I, P, P, P, P, P],
+        "hds_moe_scatter": [P, L, P, L, P, P, P, P, P, I, I, I, I, P],
+        "hds_moe_gemm": [P, L, P, L, P, I, I, I, I, I, I, I, P, L, P],
+        "hds_moe_gather": [P, L, P, P, P, L, I, I, I, I, P],
         "hds_multi_tensor_adam": [I, P, P, P, P, P, I, I, F, F, F, F, F, I, I, I, F, P],
         "hds_multi_tensor_lion": [I, P, P, P, P, I, I, F, F, F, F, F, P],
     }
@@ -64,6 +68,8 @@ def _declare_cuda(lib: ctypes.CDLL) -> None:
     lib.hds_paged_attention_prefill_workspace_bytes.restype = c_int64
     lib.hds_gemm_splitk_workspace_bytes.argtypes = [I, I]
     lib.hds_gemm_splitk_workspace_bytes.restype = c_int64
+    lib.hds_moe_padded_rows.argtypes = [I, I, I]
+    lib.hds_moe_padded_rows.restype = c_int64
     # optional entry points (declared when present so older builds keep loading)
     optional = {
         "hds_tp_barrier": ([P, I, I, P], c_int),

@@ -193,6 +193,25 @@ int hds_paged_attention_prefill(const void* q, void* out, const void* kv_cache_l
 /* Scratch bytes for n_splits > 1 (0 when n_splits <= 1). Zero it once; the kernel leaves its tickets zeroed. */
 int64_t hds_paged_attention_prefill_workspace_bytes(int n_items, int n_q_heads, int head_dim, int n_splits);
 
+/* ---- mixture of experts (tensor-parallel experts; ref ragged_ops/{top_k_gating,moe_scatter,moe_gather}, moe_gemm) --- */
+/* Per token: softmax over E logits, top-k (ties -> lower index), optional renormalisation of the k scores.
+ * counts[E] must be zero on entry (hds_moe_scatter re-zeroes it). offsets[t, j] = row claimed inside expert_ids[t, j]. */
+int hds_moe_topk_gating(const void* logits, int64_t ld_logits, int T, int E, int k, int normalize, int logits_dtype,
+                        float* scores, int32_t* expert_ids, int32_t* offsets, int32_t* counts, void* stream);
+/* pad_off[E+1]: expert row ranges rounded up to 128 rows; xs[row] = x[t] for every (t, j); mapped_slots[t, j] = row.
+ * xs needs hds_moe_padded_rows(T, E, k) rows. */
+int hds_moe_scatter(const void* x, int64_t ldx, void* xs, int64_t ld_xs, const int32_t* expert_ids,
+                    const int32_t* offsets, int32_t* counts, int32_t* pad_off, int32_t* mapped_slots, int T, int E, int k,
+                    int H, void* stream);
+int64_t hds_moe_padded_rows(int T, int E, int k);
+/* Grouped tcgen05 GEMM: rows [pad_off[e], pad_off[e+1]) of A times W_stacked[e*N:(e+1)*N, :]^T; epilogue as hds_gemm
+ * (no bias). max_rows = row capacity of A and out (multiple of 128). */
+int hds_moe_gemm(const void* A, int64_t lda, const void* W_stacked, int64_t ldw, const int32_t* pad_off, int n_experts,
+                 int max_rows, int N, int K, int dtype, int epilogue, int act, void* out, int64_t ldo, void* stream);
+/* out[t, :] += sum_j scores[t, j] * y[mapped_slots[t, j], :]   (out fp32: the pending residual delta) */
+int hds_moe_gather(const void* y, int64_t ldy, const int32_t* mapped_slots, const float* scores, float* out, int64_t ldo,
+                   int T, int k, int H, int dtype, void* stream);
+
 /* ---- fused multi-tensor optimizers (training runtime) ----------------------------------------------- */
 /* One Adam / AdamW (adamw_mode = 1: decoupled decay) or Lion step over n_tensors tensors. params / grads / exp_avg /
  * exp_avg_sq / numels are HOST arrays of device pointers and element counts. dtype codes: 0 bf16, 1 fp16, 2 fp32;

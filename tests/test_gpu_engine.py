@@ -12,7 +12,7 @@ def _cfg(T=512, S=8, ctx=1024, mem=512 * 1024 * 1024, **hc):
         "memory_config": {"mode": "allocate", "size": mem}}, hcache=hc or {"enabled": True})
 
 
-@pytest.mark.parametrize("arch", ["tiny-llama-test", "tiny-opt-test"])
+@pytest.mark.parametrize("arch", ["tiny-llama-test", "tiny-opt-test", "tiny-mixtral-test"])
 def test_gpu_matches_cpu_oracle(arch):
     from hcache_deepspeed_b200.inference.v2 import build_engine_from_arch
     from hcache_deepspeed_b200.models.arch import named_arch

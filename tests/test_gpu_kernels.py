@@ -385,3 +385,54 @@ def test_attention_prefill(dtype, n_q_heads, n_kv, d, bs):
             K().paged_attention_prefill(q, out, cache, tables, items_t, len(items), n_q_heads, n_kv, d, bs, scale,
                                         n_splits=n_splits, workspace=ws)
             torch.testing.assert_close(out.float(), want.float(), **tol(dtype))
+
+
+# ------------------------------------------------------------------------------------------------
+# mixture of experts
+# ------------------------------------------------------------------------------------------------
+@pytest.mark.parametrize("T,E,k,norm", [(1, 8, 2, True), (37, 8, 2, False), (300, 60, 4, True), (5, 3, 1, False)])
+def test_moe_pipeline(T, E, k, norm):
+    """top-k gating -> scatter -> grouped gated GEMM -> grouped GEMM -> weighted gather vs a per-token fp32 loop."""
+    torch.manual_seed(T + E)
+    H, I = 256, 384
+    kern = K()
+    x = rand(T, H)
+    w_router = rand(E, H, scale=H ** -0.5)
+    w_up = rand(E * 2 * I, H, scale=H ** -0.5)     # stacked, gate/up interleaved per expert
+    w_down = rand(E * H, I, scale=I ** -0.5)
+    logits = kern.gemm(x, w_router)
+    scores = torch.empty(T, k, dtype=torch.float32, device="cuda")
+    ids = torch.empty(T, k, dtype=torch.int32, device="cuda")
+    offs = torch.empty(T, k, dtype=torch.int32, device="cuda")
+    slots = torch.empty(T, k, dtype=torch.int32, device="cuda")
+    counts = torch.zeros(E, dtype=torch.int32, device="cuda")
+    pad_off = torch.zeros(E + 1, dtype=torch.int32, device="cuda")
+    rows = kern.moe_padded_rows(T, E, k)
+    xs = torch.zeros(rows, H, dtype=x.dtype, device="cuda")
+    hs = torch.zeros(rows, I, dtype=x.dtype, device="cuda")
+    ys = torch.zeros(rows, H, dtype=x.dtype, device="cuda")
+    out = torch.zeros(T, H, dtype=torch.float32, device="cuda")
+    for rep in range(2):  # the counters must come back zeroed
+        kern.moe_topk_gating(logits, k, norm, scores, ids, offs, counts)
+        kern.moe_scatter(x, xs, ids, offs, counts, pad_off, slots, k)
+        kern.moe_gemm(xs, w_up, pad_off, E, hs, act=3, gated=True)
+        kern.moe_gemm(hs, w_down, pad_off, E, ys)
+        out.zero_()
+        kern.moe_gather(ys, slots, scores, out)
+    torch.cuda.synchronize()
+    assert int(counts.abs().max()) == 0 and int(pad_off[-1]) % 128 == 0
+    # oracle
+    probs = torch.softmax(logits.float(), -1)
+    topv, topi = torch.topk(probs, k, dim=-1)
+    assert torch.equal(topi.int().sort(-1).values, ids.sort(-1).values)
+    if norm:
+        topv = topv / topv.sum(-1, keepdim=True)
+    torch.testing.assert_close(scores.sort(-1).values, topv.sort(-1).values, rtol=1e-4, atol=1e-5)
+    want = torch.zeros(T, H, device="cuda")
+    for t in range(T):
+        for j in range(k):
+            e = int(ids[t, j])
+            h = ref.gemm(x[t:t + 1], w_up[e * 2 * I:(e + 1) * 2 * I], act=3, gated=True, out_dtype=torch.float32).to(x.dtype)
+            y = ref.gemm(h, w_down[e * H:(e + 1) * H], out_dtype=torch.float32).to(x.dtype)
+            want[t] += float(scores[t, j]) * y[0].float()
+    torch.testing.assert_close(out, want, rtol=3e-2, atol=3e-2)
