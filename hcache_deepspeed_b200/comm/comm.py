@@ -197,7 +197,21 @@ def all_to_all_single(output, tensor, output_split_sizes=None, input_split_sizes
 
 @timed_op
 def all_to_all(output_tensor_list, input_tensor_list, group=None, async_op=False):
-    return tdist.all_to_all(output_tensor_list, input_tensor_list, group=group, async_op=async_op)
+    if tdist.get_backend(group) != "gloo":
+        return tdist.all_to_all(output_tensor_list, input_tensor_list, group=group, async_op=async_op)
+    # gloo has no list all-to-all: exchange with non-blocking point-to-point pairs
+    ws, me = tdist.get_world_size(group), tdist.get_rank(group)
+    output_tensor_list[me].copy_(input_tensor_list[me])
+    reqs = []
+    for r in range(ws):
+        if r == me:
+            continue
+        peer = tdist.get_global_rank(group, r) if group is not None else r
+        reqs.append(tdist.isend(input_tensor_list[r].contiguous(), peer, group=group))
+        reqs.append(tdist.irecv(output_tensor_list[r], peer, group=group))
+    for q in reqs:
+        q.wait()
+    return None
 
 
 @timed_op

@@ -1,0 +1,93 @@
+"""Worker functions for the MoE / sequence-parallel multi-rank tests."""
+import math
+
+import torch
+
+
+def _attn(q, k, v):
+    # q, k, v: [b, s, h, d] full sequence, causal
+    qh, kh, vh = (t.permute(0, 2, 1, 3) for t in (q, k, v))
+    s = torch.matmul(qh, kh.transpose(-1, -2)) / math.sqrt(q.shape[-1])
+    n = q.shape[1]
+    s = s.masked_fill(torch.triu(torch.ones(n, n, dtype=torch.bool), 1), float("-inf"))
+    return torch.matmul(torch.softmax(s, -1), vh).permute(0, 2, 1, 3)
+
+
+def ulysses_worker(rank, world, heads):
+    import hcache_deepspeed_b200 as ds
+    from hcache_deepspeed_b200 import comm as dist
+    from hcache_deepspeed_b200.sequence.layer import DistributedAttention
+    ds.init_distributed(dist_backend="gloo")
+    torch.manual_seed(0)
+    b, s, d = 2, 8 * world, 16
+    q, k, v = (torch.randn(b, s, heads, d) for _ in range(3))
+    want = _attn(q, k, v)
+    sl = slice(rank * s // world, (rank + 1) * s // world)
+    ql, kl, vl = (t[:, sl].clone().requires_grad_(True) for t in (q, k, v))
+    attn = DistributedAttention(_attn, dist.get_world_group())
+    out = attn(ql, kl, vl)
+    out.sum().backward()
+    qf = q.clone().requires_grad_(True)
+    _attn(qf, k, v).sum().backward()
+    return {"err": float((out - want[:, sl]).abs().max()), "gerr": float((ql.grad - qf.grad[:, sl]).abs().max())}
+
+
+def fpdt_worker(rank, world, chunks, offload):
+    import hcache_deepspeed_b200 as ds
+    from hcache_deepspeed_b200 import comm as dist
+    from hcache_deepspeed_b200.sequence.fpdt_layer import FPDT_Attention
+    ds.init_distributed(dist_backend="gloo")
+    torch.manual_seed(0)
+    b, s, h, d = 1, 8 * world * chunks, 4, 8
+    q, k, v = (torch.randn(b, s, h, d) for _ in range(3))
+    want = _attn(q, k, v)
+    sl = slice(rank * s // world, (rank + 1) * s // world)
+    out = FPDT_Attention(dist.get_world_group(), num_chunks=chunks, offloading=offload)(q[:, sl], k[:, sl], v[:, sl])
+    return {"err": float((out - want[:, sl]).abs().max())}
+
+
+class _Expert(torch.nn.Module):
+    def __init__(self, d):
+        super().__init__()
+        self.a, self.b = torch.nn.Linear(d, 2 * d), torch.nn.Linear(2 * d, d)
+
+    def forward(self, x):
+        return self.b(torch.relu(self.a(x)))
+
+
+def moe_worker(rank, world, ep_size, k):
+    """Expert-parallel MoE == the same layer with all experts local (ep=1) given identical weights and tokens."""
+    import hcache_deepspeed_b200 as ds
+    from hcache_deepspeed_b200 import comm as dist
+    from hcache_deepspeed_b200.moe.layer import MoE
+    ds.init_distributed(dist_backend="gloo")
+    d, E, tokens = 16, 4, 32
+    torch.manual_seed(3)
+    ref = MoE(d, _Expert(d), num_experts=E, ep_size=1, k=k, capacity_factor=4.0, min_capacity=4, use_rts=False,
+              top2_2nd_expert_sampling=False)
+    # give every expert distinct weights
+    for i, e in enumerate(ref.deepspeed_moe.experts.deepspeed_experts):
+        torch.manual_seed(100 + i)
+        for p in e.parameters():
+            p.data.normal_(0, 0.2)
+    torch.manual_seed(3)
+    par = MoE(d, _Expert(d), num_experts=E, ep_size=ep_size, k=k, capacity_factor=4.0, min_capacity=4, use_rts=False,
+              top2_2nd_expert_sampling=False)
+    par.set_deepspeed_parallelism()
+    par.deepspeed_moe.gate.wg.weight.data.copy_(ref.deepspeed_moe.gate.wg.weight.data)
+    ep_rank = dist.get_rank() % ep_size
+    nl = E // ep_size
+    for li, e in enumerate(par.deepspeed_moe.experts.deepspeed_experts):
+        src = ref.deepspeed_moe.experts.deepspeed_experts[ep_rank * nl + li]
+        e.load_state_dict(src.state_dict())
+    # every rank of an EP group routes its own tokens; compare each rank's output with the all-local layer on its tokens
+    torch.manual_seed(50 + rank)
+    x = torch.randn(tokens, d, requires_grad=True)
+    y, l_aux, counts = par(x)
+    y.sum().backward()
+    x2 = x.detach().clone().requires_grad_(True)
+    y2, l_aux2, counts2 = ref(x2)
+    y2.sum().backward()
+    return {"err": float((y - y2).abs().max()), "gerr": float((x.grad - x2.grad).abs().max()),
+            "laux": float(l_aux), "laux_ref": float(l_aux2), "counts": counts.tolist(),
+            "is_moe_param": all(getattr(p, "allreduce", True) is False for p in par.deepspeed_moe.experts.parameters())}

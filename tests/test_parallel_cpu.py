@@ -1,0 +1,90 @@
+"""MoE (gating + expert parallelism) and sequence parallelism (Ulysses, FPDT) on CPU ranks (gloo).
+Mirrors tests/unit/moe/test_moe.py and tests/unit/sequence_parallelism/test_ulysses.py of the reference."""
+import math
+
+import pytest
+import torch
+
+from tests.dist_utils import run_distributed
+from tests.parallel_helper import fpdt_worker, moe_worker, ulysses_worker
+
+pytestmark = pytest.mark.timeout(600)
+
+
+def test_gating_functions():
+    from hcache_deepspeed_b200.moe.sharded_moe import top1gating, top2gating, topkgating
+    torch.manual_seed(0)
+    S, E = 64, 4
+    logits = torch.randn(S, E)
+    l, combine, dispatch, counts = top1gating(logits, capacity_factor=1.0, min_capacity=4, use_rts=False)
+    C = combine.shape[2]
+    assert C == 16 and dispatch.shape == (S, E, C) and int(counts.sum()) == S
+    assert int(dispatch.sum(dim=(0, 2)).max()) <= C          # capacity respected
+    assert int(dispatch.sum(dim=(1, 2)).max()) <= 1          # a token goes to at most one slot
+    assert float(l) > 0
+    l, combine, dispatch, counts = top2gating(logits, capacity_factor=2.0, min_capacity=4, top2_2nd_expert_sampling=False)
+    per_tok = dispatch.sum(dim=(1, 2))
+    assert int(per_tok.max()) <= 2 and int(counts.sum()) == 2 * S
+    kept = per_tok == 2
+    torch.testing.assert_close(combine.sum(dim=(1, 2))[kept], torch.ones(int(kept.sum())))   # weights renormalised
+    l, combine, dispatch, counts = topkgating(logits, 3, capacity_factor=4.0, min_capacity=4)
+    assert int(dispatch.sum(dim=(1, 2)).max()) == 3 and int(dispatch.sum(dim=(1, 2)).min()) == 3
+    # each (expert, slot) holds at most one token
+    assert int(dispatch.sum(dim=0).max()) <= 1
+
+
+def test_moe_param_groups():
+    from hcache_deepspeed_b200.moe.layer import MoE
+    from hcache_deepspeed_b200.moe.utils import (has_moe_layers, is_moe_param,
+                                                 split_params_into_different_moe_groups_for_optimizer)
+    m = torch.nn.Sequential(torch.nn.Linear(8, 8), MoE(8, torch.nn.Linear(8, 8), num_experts=2, ep_size=1))
+    assert has_moe_layers(m) == (True, 2)
+    groups_ = split_params_into_different_moe_groups_for_optimizer({"params": list(m.parameters()), "lr": 0.1})
+    moe_g = [g for g in groups_ if g.get("moe")]
+    assert len(moe_g) == 1 and moe_g[0]["name"] == "ep_size_1" and all(is_moe_param(p) for p in moe_g[0]["params"])
+    assert not any(is_moe_param(p) for p in groups_[0]["params"]) and groups_[0]["lr"] == 0.1
+
+
+@pytest.mark.parametrize("world,ep,k", [(2, 2, 1), (4, 2, 2)])
+def test_expert_parallel_matches_local(world, ep, k):
+    for r in run_distributed(moe_worker, world, ep, k):
+        assert r["err"] < 1e-5 and r["gerr"] < 1e-5 and r["is_moe_param"]
+        assert r["laux"] == pytest.approx(r["laux_ref"], rel=1e-5)
+
+
+@pytest.mark.parametrize("world,heads", [(2, 4), (4, 4), (2, 5)])
+def test_ulysses_matches_full_attention(world, heads):
+    for r in run_distributed(ulysses_worker, world, heads):
+        assert r["err"] < 1e-5 and r["gerr"] < 1e-5
+
+
+@pytest.mark.parametrize("world,chunks,offload", [(2, 2, False), (2, 3, True)])
+def test_fpdt_chunked_attention(world, chunks, offload):
+    for r in run_distributed(fpdt_worker, world, chunks, offload):
+        assert r["err"] < 1e-5
+
+
+def test_update_out_and_lse_merges_blocks():
+    from hcache_deepspeed_b200.sequence.fpdt_layer import _attn_with_lse, update_out_and_lse
+    torch.manual_seed(0)
+    q, k, v = (torch.randn(1, 6, 2, 8) for _ in range(3))
+    full, _ = _attn_with_lse(q, k, v, None, 0.3)
+    o, l = None, None
+    for ks, vs in zip(k.chunk(3, dim=1), v.chunk(3, dim=1)):
+        bo, bl = _attn_with_lse(q, ks, vs, None, 0.3)
+        o, l = update_out_and_lse(o, l, bo, bl)
+    torch.testing.assert_close(o, full.float(), rtol=1e-5, atol=1e-6)
+
+
+def test_sequence_parallel_cross_entropy_single_rank():
+    from hcache_deepspeed_b200.sequence.cross_entropy import vocab_sequence_parallel_cross_entropy
+    torch.manual_seed(0)
+    logits = torch.randn(5, 2, 11, requires_grad=True)
+    tgt = torch.randint(0, 11, (5, 2))
+    loss = vocab_sequence_parallel_cross_entropy(logits, tgt, None)
+    want = torch.nn.functional.cross_entropy(logits.reshape(-1, 11), tgt.reshape(-1), reduction="none").reshape(5, 2)
+    torch.testing.assert_close(loss, want, rtol=1e-5, atol=1e-6)
+    loss.sum().backward()
+    l2 = logits.detach().clone().requires_grad_(True)
+    torch.nn.functional.cross_entropy(l2.reshape(-1, 11), tgt.reshape(-1), reduction="sum").backward()
+    torch.testing.assert_close(logits.grad, l2.grad, rtol=1e-5, atol=1e-6)
