@@ -1,0 +1,64 @@
+"""AutoTP, TP layers and shard arithmetic (reference: tests/unit/inference/test_inference.py AutoTP cases,
+tests/unit/model_parallelism/test_autotp_training.py)."""
+import pytest
+import torch
+
+from tests.autotp_helper import autotp_worker
+from tests.dist_utils import run_distributed
+
+pytestmark = pytest.mark.timeout(600)
+
+
+def test_shard_sizes_follow_heads():
+    from hcache_deepspeed_b200.module_inject import tp_shard
+    tp_shard.set_num_kv_heads(6)
+    assert tp_shard.get_shard_size_list(6 * 64, 4) == [128, 128, 64, 64]
+    assert sum(tp_shard.get_shard_size_list(6 * 64, 4)) == 384
+    assert tp_shard.get_shard_size_list(1000, 3, "lm_head") == [334, 333, 333]
+    tp_shard.set_num_kv_heads(None)
+    assert tp_shard.get_shard_size_list(10, 4) == [3, 3, 2, 2]
+
+
+def test_fused_qkv_split():
+    from hcache_deepspeed_b200.module_inject.fusedqkv_utils import prepare_tp_fused_qkvw, shard_chunk_mlp
+    from hcache_deepspeed_b200.module_inject import tp_shard
+    tp_shard.set_num_kv_heads(None)
+    h = 8
+    w = torch.arange(3 * h * 2, dtype=torch.float32).reshape(3 * h, 2)
+    parts = [prepare_tp_fused_qkvw("GLMBlock", w, 2, r) for r in range(2)]
+    q, k, v = torch.chunk(w, 3, dim=0)
+    assert torch.equal(parts[0], torch.cat([q[:4], k[:4], v[:4]])) and torch.equal(parts[1], torch.cat([q[4:], k[4:], v[4:]]))
+    wb = torch.arange(4 * 3 * 2 * 2, dtype=torch.float32).reshape(4 * 3 * 2, 2)   # 4 heads x (q,k,v) x d=2
+    p0 = prepare_tp_fused_qkvw("BloomBlock", wb, 2, 0, num_heads=4)
+    assert torch.equal(p0, wb[:12])
+    gu = torch.arange(8 * 2, dtype=torch.float32).reshape(8, 2)
+    w1, _ = shard_chunk_mlp(gu, None, 1, 2)
+    assert torch.equal(w1, torch.cat([gu[2:4], gu[6:8]]))
+
+
+def test_group_quantizer_roundtrip():
+    from hcache_deepspeed_b200.module_inject.replace_module import GroupQuantizer
+    torch.manual_seed(0)
+    w = torch.randn(64, 32)
+    q = GroupQuantizer(q_int8=True, group_size=8).quantize(w)
+    assert q.dtype == torch.int8 and q.scale.numel() == 8
+    back = GroupQuantizer.dequantize(q.data, q.scale, torch.float32)
+    assert float((back - w).abs().max()) < float(w.abs().max()) / 100
+
+
+def test_policy_table_lists_reference_containers():
+    from hcache_deepspeed_b200.module_inject.policy import policy_for, replace_policies
+    names = {p.name for p in replace_policies()}
+    for n in ("bert", "bloom", "clip", "distil_bert", "gpt2", "gptj", "gptneo", "gptneox", "internlm", "llama", "llama2",
+              "megatron_gpt", "megatron_gpt_moe", "opt", "unet", "vae"):
+        assert n in names
+    assert policy_for("llama").supported and policy_for("opt").supported and not policy_for("bloom").supported
+
+
+@pytest.mark.parametrize("world", [2, 4])
+def test_autotp_matches_unsharded(world):
+    for r in run_distributed(autotp_worker, world):
+        assert r["err"] < 1e-4
+        assert r["gems"] == ["mlp.down_proj", "self_attn.o_proj"]
+        assert r["types"] == ["LinearLayer", "LinearAllreduce", "LinearAllreduce", "LmHeadLinearAllreduce"]
+        assert r["heads"] == 4 // world and r["q_rows"] == 32 // world and r["o_cols"] == 32 // world
