@@ -1,0 +1,3 @@
+from .config import LoRAConfig, QuantizationConfig  # noqa: F401
+from .optimized_linear import LoRAOptimizedLinear, OptimizedLinear  # noqa: F401
+from .quantization import QuantizedLinear, QuantizedParameter  # noqa: F401

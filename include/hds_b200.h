@@ -212,6 +212,21 @@ int hds_moe_gemm(const void* A, int64_t lda, const void* W_stacked, int64_t ldw,
 int hds_moe_gather(const void* y, int64_t ldy, const int32_t* mapped_slots, const float* scores, float* out, int64_t ldo,
                    int T, int k, int H, int dtype, void* stream);
 
+/* ---- group-wise quantizers (ref: csrc/quantization, csrc/fp_quantizer) ------------------------------------ */
+/* dtype codes: 0 bf16, 1 fp16, 2 fp32. Integer: bits 4 or 8; params[g] = (scale, offset): value = code * scale + offset.
+ * 4-bit codes are packed two per byte (low nibble first). */
+int hds_quantize_int(const void* src, int dtype, int64_t n_groups, int group_size, int bits, int symmetric, void* dst,
+                     float* params, void* stream);
+int hds_dequantize_int(const void* src, const float* params, int64_t n_groups, int group_size, int bits, void* dst,
+                       int dtype, void* stream);
+/* Minifloat: q_bits 8 (e4m3) / 6 (e3m2) / 4 (e2m1) / 12 (e4m7), all-finite encodings, one fp32 scale per group
+ * (scale = max|x| / format max). Packed at the natural bit width. group_idx (may be NULL) selects which stored group
+ * each output group comes from (selective dequantisation). */
+int hds_fp_quantize(const void* src, int dtype, int64_t n_groups, int group_size, int q_bits, void* dst, float* scales,
+                    void* stream);
+int hds_fp_dequantize(const void* src, const float* scales, const int32_t* group_idx, int64_t n_out_groups, int group_size,
+                      int q_bits, void* dst, int dtype, void* stream);
+
 /* ---- fused multi-tensor optimizers (training runtime) ----------------------------------------------- */
 /* One Adam / AdamW (adamw_mode = 1: decoupled decay) or Lion step over n_tensors tensors. params / grads / exp_avg /
  * exp_avg_sq / numels are HOST arrays of device pointers and element counts. dtype codes: 0 bf16, 1 fp16, 2 fp32;

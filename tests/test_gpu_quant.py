@@ -1,0 +1,75 @@
+"""CUDA quantizer + fused-optimizer kernels against the torch restatements."""
+import pytest
+import torch
+
+pytestmark = [pytest.mark.gpu, pytest.mark.timeout(300)]
+
+
+@pytest.mark.parametrize("dtype", [torch.bfloat16, torch.float16, torch.float32])
+@pytest.mark.parametrize("bits,sym", [(8, True), (8, False), (4, True), (4, False)])
+def test_int_quantizer_matches_cpu(dtype, bits, sym):
+    from hcache_deepspeed_b200.ops.quantizer import dequantize_int, quantize_int
+    torch.manual_seed(0)
+    x = (torch.randn(64, 1024) * 2 + (0 if sym else 1)).to(dtype)
+    cg, pg = quantize_int(x.cuda(), 64, bits, sym)
+    cc, pc = quantize_int(x, 64, bits, sym)
+    torch.testing.assert_close(pg.cpu(), pc, rtol=1e-6, atol=1e-7)
+    diff = (cg.cpu().to(torch.int32) - cc.to(torch.int32)) if bits == 8 else None
+    if diff is not None:
+        assert int(diff.abs().max()) <= 1 and float((diff != 0).float().mean()) < 1e-3  # ties may round differently
+    back = dequantize_int(cg, pg, bits, dtype, x.shape).cpu().float()
+    assert float((back - x.float()).abs().max()) <= float(pc[:, 0].max()) * 0.51 + 1e-2 * float(x.float().abs().max())
+
+
+@pytest.mark.parametrize("q_bits", [4, 6, 8, 12])
+def test_fp_quantizer_matches_cpu(q_bits):
+    from hcache_deepspeed_b200.ops.fp_quantizer import fp_dequantize, fp_quantize
+    torch.manual_seed(1)
+    x = torch.randn(32, 512, dtype=torch.bfloat16)
+    pg, sg = fp_quantize(x.cuda(), q_bits, 512)
+    pc, sc = fp_quantize(x, q_bits, 512)
+    torch.testing.assert_close(sg.cpu(), sc)
+    assert float((pg.cpu() != pc).float().mean()) < 2e-3
+    bg = fp_dequantize(pg, sg, q_bits, 512, torch.bfloat16, x.shape).cpu().float()
+    bc = fp_dequantize(pc, sc, q_bits, 512, torch.bfloat16, x.shape).float()
+    assert float((bg - bc).abs().max()) <= float(x.float().abs().max()) * 0.26
+    idx = torch.tensor([5, 0, 31], dtype=torch.int32)
+    sel = fp_dequantize(pg, sg, q_bits, 512, torch.bfloat16, (3, 512), group_idx=idx.cuda()).cpu()
+    torch.testing.assert_close(sel.float(), bg[idx.long()])
+
+
+@pytest.mark.parametrize("pdt,gdt", [(torch.float32, torch.float32), (torch.float32, torch.bfloat16), (torch.bfloat16, torch.bfloat16)])
+@pytest.mark.parametrize("adamw", [True, False])
+def test_fused_adam_matches_torch(pdt, gdt, adamw):
+    from hcache_deepspeed_b200.ops.adam import FusedAdam
+    torch.manual_seed(2)
+    shapes = [(1000, 33), (7, ), (70001, ), (256, 256)] * 8  # > 24 tensors: several launches
+    ps = [torch.nn.Parameter(torch.randn(*s, device="cuda").to(pdt)) for s in shapes]
+    ref = [torch.nn.Parameter(p.detach().float().clone()) for p in ps]
+    opt = FusedAdam(ps, lr=1e-2, weight_decay=0.05, adam_w_mode=adamw)
+    ropt = (torch.optim.AdamW if adamw else torch.optim.Adam)(ref, lr=1e-2, weight_decay=0.05)
+    for _ in range(3):
+        for p, r in zip(ps, ref):
+            g = torch.randn_like(r)
+            p.grad = g.to(gdt)
+            r.grad = g.to(gdt).float()
+        opt.step()
+        ropt.step()
+    tol = 1e-5 if pdt == torch.float32 else 3e-2
+    for p, r in zip(ps, ref):
+        torch.testing.assert_close(p.detach().float(), r.detach(), rtol=tol, atol=tol)
+
+
+def test_fused_lion_matches_reference():
+    from hcache_deepspeed_b200.ops.lion import FusedLion
+    from hcache_deepspeed_b200.ops.lion.lion import lion_reference
+    torch.manual_seed(3)
+    p = torch.nn.Parameter(torch.randn(100000, device="cuda"))
+    w, m = p.detach().cpu().clone(), torch.zeros(100000)
+    opt = FusedLion([p], lr=1e-3, weight_decay=0.1)
+    for _ in range(3):
+        g = torch.randn(100000)
+        p.grad = g.cuda()
+        opt.step()
+        lion_reference(w, g, m, 1e-3, 0.9, 0.999, 0.1)
+    torch.testing.assert_close(p.detach().cpu(), w, rtol=1e-5, atol=1e-6)
