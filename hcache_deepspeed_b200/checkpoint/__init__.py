@@ -1,0 +1,8 @@
+"""Checkpoint tooling: consolidate ZeRO shards to fp32, convert to / load from the "universal" (parallelism-agnostic)
+format, inspect checkpoints (``deepspeed.checkpoint``)."""
+from .constants import *  # noqa: F401,F403
+from .deepspeed_checkpoint import DeepSpeedCheckpoint  # noqa: F401
+from .ds_to_universal import convert_to_universal  # noqa: F401
+from .universal_checkpoint import load_hp_checkpoint_state, load_universal_into_engine  # noqa: F401
+from .zero_to_fp32 import (convert_zero_checkpoint_to_fp32_state_dict, get_fp32_state_dict_from_zero_checkpoint,  # noqa: F401
+                           load_state_dict_from_zero_checkpoint)

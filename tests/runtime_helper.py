@@ -162,3 +162,36 @@ def pipe_reference(steps, micro_batches, dp):
         opt.zero_grad()
         losses.append(float(loss))
     return losses
+
+
+def ckpt_tools_worker(rank, world, stage, save_dir, mode):
+    """mode 'save': train a few steps with ZeRO and save; mode 'universal': resume a (different dp size) run from the
+    universal checkpoint and return the parameters + one more step's loss."""
+    import hcache_deepspeed_b200 as ds
+    ds.init_distributed(dist_backend="gloo")
+    torch.manual_seed(1234)
+    model = TinyNet(32)
+    cfg = {"train_micro_batch_size_per_gpu": 4, "optimizer": {"type": "AdamW", "params": {"lr": 1e-2, "weight_decay": 0.0}},
+           "zero_optimization": {"stage": stage, "stage3_param_persistence_threshold": 0}, "steps_per_print": 1000}
+    engine, _, _, _ = ds.initialize(model=model, config=cfg)
+    if mode == "save":
+        for x, y in make_batches(3, 4 * world, 32):
+            lo = rank * 4
+            loss = engine(x[lo:lo + 4], y[lo:lo + 4])
+            engine.backward(loss)
+            engine.step()
+        engine.save_checkpoint(save_dir, tag="t3")
+        if stage == 3:
+            from hcache_deepspeed_b200.runtime.zero import GatheredParameters
+            sd = {}
+            for n, p in engine.module.named_parameters():
+                with GatheredParameters([p]):
+                    sd[n] = p.data.detach().float().clone()
+            return sd
+        return {k: v.detach().float().clone() for k, v in engine.module.state_dict().items()}
+    from hcache_deepspeed_b200.checkpoint import load_universal_into_engine
+    n = load_universal_into_engine(engine, save_dir)
+    out = {"restored": n, "state": {k: v.detach().float().clone() for k, v in engine.module.state_dict().items()}}
+    m = engine.optimizer.single_partition_of_fp32_groups[0]
+    out["exp_avg_norm"] = float(engine.optimizer.optimizer.state[m]["exp_avg"].norm())
+    return out

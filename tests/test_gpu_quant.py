@@ -46,6 +46,9 @@ def test_fused_adam_matches_torch(pdt, gdt, adamw):
     shapes = [(1000, 33), (7, ), (70001, ), (256, 256)] * 8  # > 24 tensors: several launches
     ps = [torch.nn.Parameter(torch.randn(*s, device="cuda").to(pdt)) for s in shapes]
     ref = [torch.nn.Parameter(p.detach().float().clone()) for p in ps]
+    if pdt != gdt:
+        for p in ps:
+            p.grad_dtype = None  # low-precision gradients for fp32 master parameters
     opt = FusedAdam(ps, lr=1e-2, weight_decay=0.05, adam_w_mode=adamw)
     ropt = (torch.optim.AdamW if adamw else torch.optim.Adam)(ref, lr=1e-2, weight_decay=0.05)
     for _ in range(3):
