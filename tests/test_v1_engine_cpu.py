@@ -1,0 +1,94 @@
+"""``init_inference`` (v1 API) on CPU — BASELINE.json config 1: an OPT-shaped model, one rank, hidden states saved for a
+512-token context, KV rebuilt from them, logits compared with recompute. Also the config rules of
+``deepspeed/__init__.py:341-362`` and ``inference/config.py`` (conflicts, deprecated aliases), generate(), beams."""
+import pytest
+import torch
+
+pytestmark = pytest.mark.timeout(600)
+
+
+def _tiny_opt():
+    from transformers import OPTConfig, OPTForCausalLM
+    torch.manual_seed(0)
+    cfg = OPTConfig(vocab_size=512, hidden_size=64, num_hidden_layers=3, ffn_dim=128, num_attention_heads=4,
+                    max_position_embeddings=1024, word_embed_proj_dim=64, do_layer_norm_before=True, dropout=0.0)
+    return OPTForCausalLM(cfg).eval()
+
+
+def _tiny_llama():
+    from transformers import LlamaConfig, LlamaForCausalLM
+    torch.manual_seed(0)
+    cfg = LlamaConfig(vocab_size=300, hidden_size=64, intermediate_size=128, num_hidden_layers=2, num_attention_heads=4,
+                      num_key_value_heads=2, max_position_embeddings=512)
+    return LlamaForCausalLM(cfg).eval()
+
+
+def test_config_merge_rules(tmp_path):
+    import json
+
+    import hcache_deepspeed_b200 as ds
+    m = _tiny_llama()
+    with pytest.raises(ValueError):
+        ds.init_inference(m, config={"dtype": "fp32"}, dtype="bf16")
+    p = tmp_path / "cfg.json"
+    p.write_text(json.dumps({"dtype": "fp32", "mp_size": 1}))
+    eng = ds.init_inference(m, config=str(p))      # deprecated mp_size alias accepted
+    assert eng._config.tensor_parallel.tp_size == 1 and eng._config.dtype == torch.float32
+    with pytest.raises(ValueError):
+        ds.init_inference(m, config=3)
+    assert "replace_with_kernel_inject" in ds.default_inference_config()
+
+
+def test_uninjected_engine_is_a_passthrough():
+    import hcache_deepspeed_b200 as ds
+    m = _tiny_llama()
+    eng = ds.init_inference(m, dtype=torch.float32)
+    ids = torch.randint(0, 300, (2, 9))
+    torch.testing.assert_close(eng(input_ids=ids).logits, m(input_ids=ids).logits)
+    eng.profile_model_time()
+    eng(input_ids=ids)
+    assert len(eng.model_times()) == 1
+    with pytest.raises(NotImplementedError):
+        eng.generate(input_ids=ids, num_beams=2)
+    with pytest.raises(KeyError):
+        eng.hidden_states(0)
+    with pytest.raises(RuntimeError):
+        eng.flush(0)
+
+
+@pytest.mark.parametrize("make", [_tiny_opt, _tiny_llama])
+def test_injected_engine_matches_hf_and_restores_from_hidden_states(make):
+    import hcache_deepspeed_b200 as ds
+    hf = make()
+    vocab = hf.config.vocab_size
+    eng = ds.init_inference(hf, dtype=torch.float32, replace_with_kernel_inject=True,
+                            hcache={"enabled": True, "max_context": 1024, "max_batch_tokens": 768, "kv_memory_bytes": 64 << 20})
+    g = torch.Generator().manual_seed(1)
+    ctx = torch.randint(0, vocab, (1, 512), generator=g)
+    turn = torch.randint(0, vocab, (1, 16), generator=g)
+    with torch.no_grad():
+        want_ctx = hf(input_ids=ctx).logits
+        want_turn = hf(input_ids=torch.cat([ctx, turn], dim=1)).logits[:, 512:]
+    out = eng(input_ids=ctx, session_ids=[7])
+    torch.testing.assert_close(out.logits, want_ctx, rtol=2e-3, atol=2e-3)
+    lat = eng.hidden_states(7)
+    assert lat.shape == (hf.config.num_hidden_layers, 512, hf.config.hidden_size)
+    live = eng(input_ids=turn, session_ids=[7]).logits            # continuation over the live KV cache
+    torch.testing.assert_close(live, want_turn, rtol=2e-3, atol=2e-3)
+    # end of turn: drop the KV cache, come back later, rebuild it from the saved hidden states instead of recomputing
+    eng.flush(7)
+    eng.restore_hidden_states(7, ctx, lat)
+    restored = eng(input_ids=turn, session_ids=[7]).logits
+    assert float((restored - want_turn).abs().max()) < 1e-3          # restore-vs-recompute (BASELINE config 1)
+    torch.testing.assert_close(restored, live, rtol=1e-4, atol=1e-4)
+
+
+def test_injected_generate_greedy_matches_hf():
+    import hcache_deepspeed_b200 as ds
+    hf = _tiny_llama()
+    eng = ds.init_inference(hf, dtype=torch.float32, replace_with_kernel_inject=True,
+                            hcache={"max_context": 256, "max_batch_tokens": 256, "kv_memory_bytes": 16 << 20})
+    ids = torch.randint(0, 300, (2, 12), generator=torch.Generator().manual_seed(3))
+    got = eng.generate(input_ids=ids, max_new_tokens=8, do_sample=False)
+    want = hf.generate(input_ids=ids, max_new_tokens=8, do_sample=False, pad_token_id=0)
+    assert torch.equal(got[:, :20], want[:, :20])
