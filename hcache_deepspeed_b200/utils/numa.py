@@ -1,0 +1,53 @@
+"""NUMA helpers for the launcher's ``--bind_cores_to_rank`` (``deepspeed/utils/numa.py:24-200``): discover nodes and
+build the ``numactl`` prefix that pins a local rank to its share of the cores."""
+from __future__ import annotations
+
+import os
+import re
+import subprocess
+from typing import List, Optional, Tuple
+
+
+def get_numa_cores() -> List[List[int]]:
+    try:
+        out = subprocess.check_output(["numactl", "--hardware"], stderr=subprocess.DEVNULL).decode()
+        nodes = []
+        for line in out.splitlines():
+            m = re.match(r"node (\d+) cpus: (.*)", line)
+            if m:
+                nodes.append([int(c) for c in m.group(2).split()])
+        if nodes:
+            return nodes
+    except (OSError, subprocess.CalledProcessError):
+        pass
+    return [list(range(os.cpu_count() or 1))]
+
+
+def parse_range_list(s: str) -> List[int]:
+    """"0-3,8,10-11" -> [0,1,2,3,8,10,11] (strictly increasing)."""
+    out = []
+    for part in s.split(","):
+        if "-" in part:
+            a, b = part.split("-")
+            a, b = int(a), int(b)
+            if b < a:
+                raise ValueError(f"invalid range {part}")
+            out += list(range(a, b + 1))
+        else:
+            out.append(int(part))
+    if any(out[i] >= out[i + 1] for i in range(len(out) - 1)):
+        raise ValueError("core list must be strictly increasing")
+    return out
+
+
+def get_numactl_cmd(bind_core_list: Optional[str], num_local_procs: int, local_rank: int) -> Tuple[int, List[str]]:
+    cores = parse_range_list(bind_core_list) if bind_core_list else list(range(os.cpu_count() or 1))
+    per = max(1, len(cores) // num_local_procs)
+    mine = cores[per * local_rank:per * (local_rank + 1)]
+    cmd = ["numactl"]
+    nodes = get_numa_cores()
+    owning = [i for i, n in enumerate(nodes) if set(mine) <= set(n)]
+    if owning:
+        cmd += ["-m", str(owning[0])]
+    cmd += ["-C", ",".join(map(str, mine))]
+    return per, cmd
