@@ -91,3 +91,45 @@ def moe_worker(rank, world, ep_size, k):
     return {"err": float((y - y2).abs().max()), "gerr": float((x.grad - x2.grad).abs().max()),
             "laux": float(l_aux), "laux_ref": float(l_aux2), "counts": counts.tolist(),
             "is_moe_param": all(getattr(p, "allreduce", True) is False for p in par.deepspeed_moe.experts.parameters())}
+
+
+def onebit_worker(rank, world):
+    """Compressed all-reduce approximates the mean and its error feedback keeps the long-run average unbiased."""
+    import hcache_deepspeed_b200 as ds
+    from hcache_deepspeed_b200.runtime.comm.compressed import CompressedBackend
+    ds.init_distributed(dist_backend="gloo")
+    b = CompressedBackend()
+    torch.manual_seed(rank)
+    n = 1000
+    we, se = torch.zeros(b.padded_size(n)), torch.zeros(b.padded_size(n) // world)
+    acc_c, acc_t = torch.zeros(n), torch.zeros(n)
+    for it in range(60):
+        g = torch.randn(n) + 0.5
+        exact = g.clone()
+        ds.comm.all_reduce(exact)
+        exact /= world
+        m = g.clone()
+        b.compressed_allreduce(m, we, se)
+        acc_c += m
+        acc_t += exact
+    return {"rel": float((acc_c - acc_t).norm() / acc_t.norm()), "same": float(m.sum())}
+
+
+def onebit_adam_worker(rank, world):
+    import hcache_deepspeed_b200 as ds
+    ds.init_distributed(dist_backend="gloo")
+    from tests.runtime_helper import TinyNet, make_batches
+    torch.manual_seed(1234)
+    cfg = {"train_micro_batch_size_per_gpu": 4, "optimizer": {"type": "OneBitAdam", "params": {"lr": 5e-3, "freeze_step": 6}},
+           "steps_per_print": 1000}
+    engine, _, _, _ = ds.initialize(model=TinyNet(32), config=cfg)
+    losses = []
+    x, y = make_batches(1, 4 * world, 32)[0]      # one fixed batch: the loss must go down
+    for _ in range(14):
+        lo = rank * 4
+        loss = engine(x[lo:lo + 4], y[lo:lo + 4])
+        engine.backward(loss)
+        engine.step()
+        losses.append(float(loss.detach()))
+    return {"losses": losses, "frozen": engine.basic_optimizer.adam_freeze_key, "allreduce_off": not engine.enable_backward_allreduce,
+            "w": engine.module.head.weight.detach().clone()}

@@ -1,0 +1,194 @@
+"""Smaller subsystems: compression, autotuning, 1-bit communication/optimizers, NVMe swapping, Megatron checkpoint
+re-sharding, sparse-attention layouts, Evoformer attention, accelerator / op-builder surfaces, data sampling."""
+import math
+import os
+import types
+
+import numpy as np
+import pytest
+import torch
+
+from tests.dist_utils import run_distributed
+from tests.parallel_helper import onebit_adam_worker, onebit_worker
+
+pytestmark = pytest.mark.timeout(600)
+
+
+class _MLP(torch.nn.Module):
+    def __init__(self):
+        super().__init__()
+        self.fc1, self.fc2 = torch.nn.Linear(16, 32), torch.nn.Linear(32, 8)
+
+    def forward(self, x):
+        return self.fc2(torch.relu(self.fc1(x)))
+
+
+def test_compression_schedule_and_clean():
+    from hcache_deepspeed_b200.compression import compression_scheduler, init_compression, redundancy_clean
+    from hcache_deepspeed_b200.compression.basic_layer import LinearLayer_Compress
+    from hcache_deepspeed_b200.compression.compress import get_compression_config
+    cfg = {"compression_training": {
+        "weight_quantization": {"shared_parameters": {"enabled": True, "schedule_offset": 2, "quantize_groups": 1,
+                                                      "quantization_type": "symmetric"},
+                                "different_groups": {"g": {"params": {"start_bits": 8, "target_bits": 4, "quantization_period": 10},
+                                                           "modules": ["fc"]}}},
+        "row_pruning": {"shared_parameters": {"enabled": True, "schedule_offset": 0, "method": "l1"},
+                        "different_groups": {"r": {"params": {"dense_ratio": 0.5}, "modules": ["fc1"], "related_modules": [["fc2"]]}}},
+        "sparse_pruning": {"shared_parameters": {"enabled": True, "schedule_offset": 1, "method": "l1"},
+                           "different_groups": {"s": {"params": {"dense_ratio": 0.25}, "modules": ["fc2"]}}}}}
+    torch.manual_seed(0)
+    m = _MLP()
+    init_compression(m, cfg)
+    assert isinstance(m.fc1, LinearLayer_Compress) and isinstance(m.fc2, LinearLayer_Compress)
+    sch = compression_scheduler(m, get_compression_config(cfg))
+    x = torch.randn(4, 16)
+    sch.step()
+    assert m.fc1.row_pruning_enabled and m.fc2.sparse_pruning_enabled and not m.fc1.weight_quantization_enabled
+    y = m(x)
+    assert int((m.fc1(x) == 0).all(dim=0).sum()) >= 16          # half of fc1's rows are masked
+    sch.step()
+    sch.step()
+    assert m.fc1.weight_quantization_enabled
+    m(x).sum().backward()
+    assert m.fc1.weight.grad is not None                          # straight-through estimator
+    redundancy_clean(m, cfg)
+    assert m.fc1.weight.shape == (16, 16) and m.fc2.weight.shape == (8, 16) and m(x).shape == (4, 8)
+    assert len(m.fc2.weight.unique()) <= 17 and float((m.fc2.weight == 0).float().mean()) >= 0.5
+
+
+def test_autotuner_picks_best_feasible_config(tmp_path):
+    from hcache_deepspeed_b200.autotuning import Autotuner
+
+    def run(cfg):
+        z, mbs = cfg["zero_optimization"]["stage"], cfg["train_micro_batch_size_per_gpu"]
+        return None if (z <= 1 and mbs > 4) else mbs * 10 - z * 3            # OOM for big batches without ZeRO-2+
+
+    for tuner in ("gridsearch", "random", "model_based"):
+        a = Autotuner({"fp16": {"enabled": True}, "autotuning": {"tuner_type": tuner, "num_tuning_micro_batch_sizes": 4,
+                                                                  "tuner_early_stopping": 100}},
+                      num_params=int(30e9), num_gpus=8, run_fn=run)
+        assert a.feasible_stages() == [1, 2, 3]                              # 30B fp16 states: 600 GB unpartitioned
+        best = a.tune()
+        assert (best["zero_optimization"]["stage"], best["train_micro_batch_size_per_gpu"]) == (2, 8) and a.best_metric == 74
+        assert os.path.exists(a.write_optimal_config(str(tmp_path / f"{tuner}.json")))
+
+
+def test_onebit_compressed_allreduce_two_ranks():
+    res = run_distributed(onebit_worker, 2)
+    assert res[0]["rel"] < 0.15 and res[0]["same"] == pytest.approx(res[1]["same"])
+
+
+def test_onebit_adam_trains_and_freezes():
+    res = run_distributed(onebit_adam_worker, 2)
+    for r in res:
+        assert r["frozen"] and r["allreduce_off"] and all(math.isfinite(l) for l in r["losses"])
+    mean = [(res[0]["losses"][i] + res[1]["losses"][i]) / 2 for i in range(14)]
+    assert mean[-1] < 0.7 * mean[0]
+    assert float((res[0]["w"] - res[1]["w"]).abs().max()) < 0.05           # replicas stay close under 1-bit momentum
+
+
+def test_nvme_swappers(tmp_path):
+    from hcache_deepspeed_b200.io.aio import aio_handle
+    from hcache_deepspeed_b200.runtime.swap_tensor import AsyncPartitionedParameterSwapper, AsyncTensorSwapper
+    sw = AsyncPartitionedParameterSwapper(model_dtype=torch.float32, nvme_path=str(tmp_path), buffer_count=3, buffer_size=1 << 20,
+                                          aio_config={"block_size": 4096})
+    sw.min_aio_bytes = 0
+    ps = []
+    for i in range(2):
+        t = torch.randn(5000 + i)
+        t.ds_numel = t.numel()
+        ps.append(types.SimpleNamespace(ds_id=i, ds_tensor=t))
+    want = [p.ds_tensor.clone() for p in ps]
+    sw.swap_out_and_release(ps)
+    assert ps[0].ds_tensor.numel() == 1 and sw.available_swap_in_buffers() == 3
+    sw.swap_in(ps, async_op=True)
+    sw.synchronize_reads()
+    for p, w in zip(ps, want):
+        assert torch.equal(p.ds_tensor.data, w)
+    ats = AsyncTensorSwapper(aio_handle(4096, 8, False, True, 1), 256)
+    ats.add_buffers([torch.empty(1 << 16) for _ in range(2)])
+    ts = [torch.randn(3000) for _ in range(40)]
+    paths = [str(tmp_path / f"t{i}.swp") for i in range(40)]
+    ats.swap_out_tensors(ts, paths)
+    ats.release_buffers()
+    assert torch.equal(torch.from_numpy(np.fromfile(paths[17], dtype=np.float32)[:3000]), ts[17])
+
+
+def test_megatron_state_dict_split_then_merge(tmp_path):
+    from hcache_deepspeed_b200.runtime.state_dict_factory import MegatronSDLoader
+    full = {"attention.query_key_value.weight": torch.arange(24.).reshape(12, 2), "attention.dense.weight": torch.arange(16.).reshape(4, 4),
+            "mlp.dense_h_to_4h.weight": torch.arange(32.).reshape(8, 4), "mlp.dense_4h_to_h.weight": torch.arange(32.).reshape(4, 8),
+            "ln.weight": torch.ones(4)}
+    torch.save({"module": full}, tmp_path / "mp0.pt")
+    loader = MegatronSDLoader([str(tmp_path / "mp0.pt")], 0)
+    parts = [loader.load(2, r)[1]["module"] for r in range(2)]
+    assert parts[0]["attention.dense.weight"].shape == (4, 2) and parts[0]["attention.query_key_value.weight"].shape == (6, 2)
+    for r in range(2):
+        torch.save({"module": parts[r]}, tmp_path / f"s{r}.pt")
+    merged = MegatronSDLoader([str(tmp_path / "s0.pt"), str(tmp_path / "s1.pt")], 0).load(1, 0)[1]["module"]
+    for k in full:
+        assert torch.equal(merged[k], full[k]), k
+
+
+def test_sparse_attention_layouts_and_op():
+    from hcache_deepspeed_b200.ops.sparse_attention import (BigBirdSparsityConfig, BSLongformerSparsityConfig, DenseSparsityConfig,
+                                                            FixedSparsityConfig, LocalSlidingWindowSparsityConfig,
+                                                            SparseSelfAttention, VariableSparsityConfig)
+    fixed = FixedSparsityConfig(2, block=4, num_local_blocks=2, attention="unidirectional").make_layout(32)
+    assert fixed.shape == (2, 8, 8) and torch.equal(fixed[0], torch.tril(fixed[0])) and int(fixed[0, 3, 2]) == 1
+    for cfg in (VariableSparsityConfig(2, block=4, local_window_blocks=[2]), BigBirdSparsityConfig(2, block=4),
+                BSLongformerSparsityConfig(2, block=4), LocalSlidingWindowSparsityConfig(2, block=4)):
+        lay = cfg.make_layout(32)
+        assert lay.shape == (2, 8, 8) and all(int(lay[0, i, i]) == 1 for i in range(8))
+    with pytest.raises(ValueError):
+        DenseSparsityConfig(2, block=4).make_layout(30)
+    q, k, v = (torch.randn(1, 2, 16, 8) for _ in range(3))
+    att = SparseSelfAttention(DenseSparsityConfig(2, block=4), max_seq_length=32)
+    torch.testing.assert_close(att(q, k, v), torch.nn.functional.scaled_dot_product_attention(q, k, v))
+    local = SparseSelfAttention(LocalSlidingWindowSparsityConfig(2, block=4, num_sliding_window_blocks=1), max_seq_length=32)
+    out = local(q, k, v)     # block-diagonal, block-causal: the first block never sees later tokens
+    want0 = torch.nn.functional.scaled_dot_product_attention(q[:, :, :4], k[:, :, :4], v[:, :, :4])
+    torch.testing.assert_close(out[:, :, :4], want0)
+
+
+def test_evoformer_attention_matches_manual():
+    from hcache_deepspeed_b200.ops.deepspeed4science import DS4Sci_EvoformerAttention
+    torch.manual_seed(0)
+    Q, K, V = (torch.randn(1, 3, 6, 2, 4) for _ in range(3))
+    b1, b2 = torch.randn(1, 3, 1, 1, 6), torch.randn(1, 1, 2, 6, 6)
+    out = DS4Sci_EvoformerAttention(Q, K, V, [b1, b2])
+    q, k, v = (t.permute(0, 1, 3, 2, 4) for t in (Q, K, V))
+    s = q @ k.transpose(-1, -2) / 2.0 + b1 + b2
+    want = (torch.softmax(s, -1) @ v).permute(0, 1, 3, 2, 4)
+    torch.testing.assert_close(out, want, rtol=1e-5, atol=1e-5)
+
+
+def test_accelerator_and_op_builders():
+    from hcache_deepspeed_b200.accelerator import get_accelerator
+    from hcache_deepspeed_b200.ops.op_builder import ALL_OPS, CPUAdamBuilder
+    acc = get_accelerator()
+    assert acc.communication_backend_name() in ("nccl", "gloo") and acc.is_available()
+    assert len(ALL_OPS) >= 20 and CPUAdamBuilder().load() is not None and ALL_OPS["async_io"].is_compatible()
+
+
+def test_curriculum_sampler_and_random_ltd():
+    from hcache_deepspeed_b200.runtime.data_pipeline.data_sampler import DeepSpeedDataSampler
+    from hcache_deepspeed_b200.runtime.data_pipeline.random_ltd import RandomLayerTokenDrop, RandomLTDScheduler
+    cfg = {"data_sampling": {"curriculum_learning": {"enabled": True, "curriculum_metrics": {"len": {
+        "min_difficulty": 2, "max_difficulty": 10, "schedule_type": "fixed_linear",
+        "schedule_config": {"total_curriculum_step": 5, "difficulty_step": 1}}}}}}
+    diff = np.arange(100) % 11
+    s = DeepSpeedDataSampler(cfg, 100, 2, 0, 2, difficulties={"len": diff})
+    it = iter(s)
+    first = next(it)
+    assert len(first) == 2 and all(diff[i] <= 2 for i in first)
+    sd = s.state_dict()
+    s.load_state_dict(sd)
+    sched = RandomLTDScheduler({"total_layer_num": 4, "random_ltd_layer_num": 2, "global_batch_size": 2,
+                                "random_ltd_schedule": {"min_value": 4, "max_value": 16, "schedule_config": {"require_steps": 10, "seq_per_step": 4}}})
+    assert sched.update_seq(0) == 4 and sched.update_seq(5) == 8 and sched.update_seq(100) == 16
+    sched.set_current_seq(4)
+    layer = RandomLayerTokenDrop(torch.nn.Linear(8, 8), scheduler=sched).train()
+    x = torch.randn(2, 16, 8)
+    y = layer(x)
+    assert y.shape == x.shape and int((y == x).all(-1).sum()) == 2 * 12      # 12 of 16 tokens per sample skipped the layer
