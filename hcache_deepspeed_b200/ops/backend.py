@@ -165,9 +165,11 @@ MAX_PREFILL_SPLITS = 16
 
 
 def pick_decode_splits(n_items: int, n_kv_heads: int, max_kv_len: int) -> int:
-    """KV splits for the split-KV kernel: enough CTAs for ~2 per SM, at least 2 tiles (256 keys) each."""
+    """KV splits for the split-KV kernel: split only while (items x kv heads x splits) stays within one CTA per SM —
+    measured (profiles/kernel_bench_attn_warps.txt): 32 CTAs -> 4 splits, 64 -> 2, >= 128 -> none; each split keeps at
+    least 2 tiles (256 keys)."""
     ctas = max(1, n_items * n_kv_heads)
-    want = max(1, (2 * N_SM + ctas - 1) // ctas)
+    want = max(1, N_SM // ctas)
     tiles = max(1, (max_kv_len + 127) // 128)
     return int(max(1, min(want, MAX_DECODE_SPLITS, tiles // 2 if tiles >= 2 else 1)))
 

@@ -18,10 +18,13 @@
 
 namespace hds {
 
-constexpr int kAttnConsumerWarps = 8;
-constexpr int kAttnThreads = (kAttnConsumerWarps + 1) * 32;  // 8 consumer warps + 1 TMA producer warp
-constexpr int kAttnTok = 128;                                 // KV tokens per pipeline stage
+// W consumer warps + 1 TMA producer warp; every consumer warp owns a 16-token strip, so a pipeline stage holds
+// 16 * W KV tokens. W = 8: 128-token tiles, 192 KB of stages, one CTA per SM. W = 4: 64-token tiles, 96 KB, TWO CTAs
+// per SM — same warps and bytes in flight per SM, but twice as many CTA slots, which removes the wave-quantisation
+// loss when (items x kv heads x splits) is not a multiple of the SM count (e.g. 8 sequences x 32 heads = 256 CTAs).
 constexpr int kAttnStages = 3;
+__host__ __device__ constexpr int attn_threads(int w) { return (w + 1) * 32; }
+__host__ __device__ constexpr int attn_tok(int w) { return 16 * w; }
 
 struct AttnArgs {
     const void* q;
@@ -35,15 +38,16 @@ struct AttnArgs {
     int32_t* counters;  // [n_items][n_kv_heads]
     float* ws_ml;       // [n_items][n_kv_heads][n_splits][R][2]
     float* ws_o;        // [n_items][n_kv_heads][n_splits][R][D]
+    int consumer_warps; // 8 (one CTA per SM) or 4 (two CTAs per SM); host-side choice, see attn_pick_warps
 };
 
-template <int D>
+template <int D, int W>
 __host__ __device__ constexpr size_t attn_stage_bytes() {
-    return static_cast<size_t>(2) * kAttnTok * D * 2;  // K + V
+    return static_cast<size_t>(2) * attn_tok(W) * D * 2;  // K + V
 }
-template <int D, int R>
+template <int D, int R, int W>
 __host__ __device__ constexpr size_t attn_smem_bytes() {
-    return kAttnStages * attn_stage_bytes<D>() + static_cast<size_t>(R) * D * 4 /*q*/ + 512 + 1024;
+    return kAttnStages * attn_stage_bytes<D, W>() + static_cast<size_t>(R) * D * 4 /*q*/ + 512 + 1024;
 }
 
 __device__ __forceinline__ float ex2f(float x) {
@@ -56,9 +60,12 @@ __device__ __forceinline__ float ex2f(float x) {
 // the q.K^T and the P.V step and keeps its own running (max, sum, accumulator); the eight partial states are
 // merged once at the end. Nothing in the main loop synchronises the CTA: warps wait on the stage's TMA
 // mbarrier and release the stage through a second mbarrier that the producer warp waits on.
-template <int D, int R, bool kBf16>
-__global__ void __launch_bounds__(kAttnThreads, 1)
+template <int D, int R, bool kBf16, int W>
+__global__ void __launch_bounds__(attn_threads(W), W == 8 ? 1 : 2)
 paged_attn_splitkv_kernel(const __grid_constant__ CUtensorMap tmap_kv, const AttnArgs a) {
+    constexpr int kAttnConsumerWarps = W;
+    constexpr int kAttnThreads = attn_threads(W);
+    constexpr int kAttnTok = attn_tok(W);
     constexpr int PANELS = D / 64;                 // 128-byte column panels per row
     constexpr int PANEL_BYTES = kAttnTok * 128;    // one panel of a 128-token tile
     constexpr int TILE_BYTES = PANELS * PANEL_BYTES;
@@ -69,7 +76,7 @@ paged_attn_splitkv_kernel(const __grid_constant__ CUtensorMap tmap_kv, const Att
     extern __shared__ uint8_t smem_raw[];
     uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
     uint8_t* stages = smem;
-    float* q_s = reinterpret_cast<float*>(smem + kAttnStages * attn_stage_bytes<D>());  // [R][D], pre-scaled
+    float* q_s = reinterpret_cast<float*>(smem + kAttnStages * attn_stage_bytes<D, W>());  // [R][D], pre-scaled
     uint64_t* full_bar = reinterpret_cast<uint64_t*>(q_s + R * D);
     uint64_t* empty_bar = full_bar + kAttnStages;
     int* flag_s = reinterpret_cast<int*>(empty_bar + kAttnStages);
@@ -126,21 +133,24 @@ paged_attn_splitkv_kernel(const __grid_constant__ CUtensorMap tmap_kv, const Att
             uint32_t stage = 0, phase = 0;
             for (int ti = t0; ti < t1; ++ti) {
                 mbar_wait(&empty_bar[stage], phase ^ 1);
-                uint8_t* kdst = stages + stage * attn_stage_bytes<D>();
+                uint8_t* kdst = stages + stage * attn_stage_bytes<D, W>();
                 uint8_t* vdst = kdst + TILE_BYTES;
                 const int tok0 = ti * kAttnTok;
                 const int n_tok = min(kAttnTok, kv_len - tok0);
-                const int nb = (n_tok + bs - 1) / bs;
-                mbar_expect_tx(&full_bar[stage], static_cast<uint32_t>(nb) * bs * D * 2 * 2);
+                const int box = bs < kAttnTok ? bs : kAttnTok;   // rows per TMA box (host builds the map with it)
+                const int nb = (n_tok + box - 1) / box;
+                mbar_expect_tx(&full_bar[stage], static_cast<uint32_t>(nb) * box * D * 2 * 2);
                 for (int b = 0; b < nb; ++b) {
-                    const int blk = table[tok0 / bs + b];
-                    const int krow = ((blk * 2 + 0) * a.n_kv_heads + kvh) * bs;
-                    const int vrow = ((blk * 2 + 1) * a.n_kv_heads + kvh) * bs;
+                    const int tok = tok0 + b * box;
+                    const int blk = table[tok / bs];
+                    const int in_blk = tok % bs;
+                    const int krow = ((blk * 2 + 0) * a.n_kv_heads + kvh) * bs + in_blk;
+                    const int vrow = ((blk * 2 + 1) * a.n_kv_heads + kvh) * bs + in_blk;
 #pragma unroll
                     for (int p = 0; p < PANELS; ++p) {
-                        tma_load_2d(kdst + p * PANEL_BYTES + b * bs * 128, &tmap_kv, &full_bar[stage], p * 64, krow,
+                        tma_load_2d(kdst + p * PANEL_BYTES + b * box * 128, &tmap_kv, &full_bar[stage], p * 64, krow,
                                     kEvictFirst);
-                        tma_load_2d(vdst + p * PANEL_BYTES + b * bs * 128, &tmap_kv, &full_bar[stage], p * 64, vrow,
+                        tma_load_2d(vdst + p * PANEL_BYTES + b * box * 128, &tmap_kv, &full_bar[stage], p * 64, vrow,
                                     kEvictFirst);
                     }
                 }
@@ -161,7 +171,7 @@ paged_attn_splitkv_kernel(const __grid_constant__ CUtensorMap tmap_kv, const Att
         }
         uint32_t stage = 0, phase = 0;
         for (int ti = t0; ti < t1; ++ti) {
-            const uint8_t* ktile = stages + stage * attn_stage_bytes<D>();
+            const uint8_t* ktile = stages + stage * attn_stage_bytes<D, W>();
             const uint8_t* vtile = ktile + TILE_BYTES;
             const int tok0 = ti * kAttnTok;
             const int n_tok = min(kAttnTok, kv_len - tok0);
@@ -327,20 +337,27 @@ paged_attn_splitkv_kernel(const __grid_constant__ CUtensorMap tmap_kv, const Att
 
 static inline int64_t align256(int64_t x) { return (x + 255) & ~int64_t(255); }
 
-template <int D, int R, bool kBf16>
-static int launch_splitkv(const CUtensorMap& tm, const AttnArgs& a, int n_items, cudaStream_t s) {
-    auto kern = paged_attn_splitkv_kernel<D, R, kBf16>;
+template <int D, int R, bool kBf16, int W>
+static int launch_splitkv_w(const CUtensorMap& tm, const AttnArgs& a, int n_items, cudaStream_t s) {
+    constexpr int kAttnThreads = attn_threads(W);
+    auto kern = paged_attn_splitkv_kernel<D, R, kBf16, W>;
     static bool configured[64] = {false};
     int dev = 0;
     cudaGetDevice(&dev);
     if (!configured[dev & 63]) {
         HDS_CHECK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                            static_cast<int>(attn_smem_bytes<D, R>())));
+                                            static_cast<int>(attn_smem_bytes<D, R, W>())));
         configured[dev & 63] = true;
     }
     dim3 grid(n_items, a.n_kv_heads, a.n_splits);
-    HDS_CHECK_CUDA(launch_kernel(kern, grid, dim3(kAttnThreads), attn_smem_bytes<D, R>(), s, tm, a));
+    HDS_CHECK_CUDA(launch_kernel(kern, grid, dim3(kAttnThreads), attn_smem_bytes<D, R, W>(), s, tm, a));
     return HDS_OK;
+}
+
+template <int D, int R, bool kBf16>
+static int launch_splitkv(const CUtensorMap& tm, const AttnArgs& a, int n_items, cudaStream_t s) {
+    return a.consumer_warps == 4 ? launch_splitkv_w<D, R, kBf16, 4>(tm, a, n_items, s)
+                                 : launch_splitkv_w<D, R, kBf16, 8>(tm, a, n_items, s);
 }
 
 template <int D, bool kBf16>
@@ -352,6 +369,15 @@ static int dispatch_rows(int rmax, const CUtensorMap& tm, const AttnArgs& a, int
 }
 
 static inline int rows_bucket(int r) { return r <= 1 ? 1 : r <= 2 ? 2 : r <= 4 ? 4 : 8; }
+
+// Measured on B200 (profiles/kernel_bench_attn_warps.txt): with more CTAs than SMs the two-CTAs-per-SM variant is
+// 2-8 % faster (8 seqs x 32 heads x 4K ctx: 101 -> 93 us; 16 seqs: 196 -> 181 us) because a second CTA fills the SM
+// while the first drains; with fewer CTAs than SMs the bigger tile wins (each CTA is alone on its SM anyway).
+static inline int attn_pick_warps(int64_t ctas) {
+    static const int forced = getenv("HDS_ATTN_WARPS") ? atoi(getenv("HDS_ATTN_WARPS")) : 0;
+    if (forced == 4 || forced == 8) return forced;
+    return ctas > sm_count() ? 4 : 8;
+}
 
 }  // namespace hds
 
@@ -404,8 +430,10 @@ extern "C" int hds_paged_attention_splitkv(const void* q, void* out, const void*
     a.ws_o = reinterpret_cast<float*>(ws + align256(units * 4) + align256(units * n_splits * R * 2 * 4));
     CUtensorMap tm;
     const uint64_t rows = static_cast<uint64_t>(num_blocks) * 2 * n_kv_heads * block_size;
-    int rc = make_tmap_2d_16b(&tm, kv_cache_layer, head_dim, rows, static_cast<uint64_t>(head_dim) * 2, 64, block_size,
-                              dtype == 0);
+    a.consumer_warps = attn_pick_warps(units * n_splits);
+    const int tile_tok = attn_tok(a.consumer_warps);
+    int rc = make_tmap_2d_16b(&tm, kv_cache_layer, head_dim, rows, static_cast<uint64_t>(head_dim) * 2, 64,
+                              block_size < tile_tok ? block_size : tile_tok, dtype == 0);
     if (rc) return rc;
     cudaStream_t s = static_cast<cudaStream_t>(stream);
     if (head_dim == 128)

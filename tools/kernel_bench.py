@@ -147,7 +147,7 @@ def bench_restore():
 
 def bench_attention_decode():
     d, bs = 128, 64
-    for (n_seqs, ctx, nq, nkv) in [(16, 4096, 32, 32), (64, 4096, 32, 32), (8, 16384, 32, 32), (64, 4096, 8, 1), (1, 4096, 32, 32)]:
+    for (n_seqs, ctx, nq, nkv) in [(8, 4096, 32, 32), (16, 4096, 32, 32), (64, 4096, 32, 32), (8, 16384, 32, 32), (64, 4096, 8, 1), (1, 4096, 32, 32), (4, 4096, 32, 32)]:
         blocks_per_seq = (ctx + 1 + bs - 1) // bs
         nb = n_seqs * blocks_per_seq
         cache = (torch.randn(nb, 2, nkv, bs, d, device=dev) * 0.3).to(torch.bfloat16)
@@ -163,7 +163,7 @@ def bench_attention_decode():
             ws = torch.zeros(max(16, K.splitkv_workspace_bytes(n_seqs, nq, nkv, d, splits, G)), dtype=torch.uint8, device=dev)
             med, mn = timeit(lambda: K.paged_attention_splitkv(q, out, cache, tables, items, n_seqs, G, nq, nkv, d, bs, splits,
                                                                 1 / math.sqrt(d), ws))
-            report(f"attn_decode seqs{n_seqs} ctx{ctx} heads{nq}/{nkv} splits{splits}", med, mn, bytes_=kv_bytes)
+            report(f"attn_decode seqs{n_seqs} ctx{ctx} heads{nq}/{nkv} splits{splits} warps{os.environ.get('HDS_ATTN_WARPS', 'auto')}", med, mn, bytes_=kv_bytes)
 
 
 def bench_attention_prefill():
