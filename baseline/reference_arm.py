@@ -52,7 +52,9 @@ def run_reference_arm(a) -> None:
     dev = torch.device("cuda", local)
     os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
     os.environ.setdefault("MASTER_PORT", "29511")
-    B, ctx, n_new, D = a.sessions * world, a.ctx, a.new_tokens, a.decode_steps
+    tp = world if getattr(a, "parallelism", "dp") == "tp" else 1   # same layout as the other arm: dp = one replica per GPU
+    replicas = world // tp
+    B, ctx, n_new, D = a.sessions * tp, a.ctx, a.new_tokens, a.decode_steps
     try:
         cfg = LlamaConfig(vocab_size=32000, max_position_embeddings=ctx + n_new + D + 64, **LLAMA[a.model])
         torch.manual_seed(1234)
@@ -64,7 +66,7 @@ def run_reference_arm(a) -> None:
             model = LlamaForCausalLM(cfg)
         torch.set_default_dtype(torch.float32)
         model = model.eval()
-        engine = deepspeed.init_inference(model, dtype=torch.bfloat16, tensor_parallel={"tp_size": world},
+        engine = deepspeed.init_inference(model, dtype=torch.bfloat16, tensor_parallel={"tp_size": tp},
                                           replace_with_kernel_inject=False)
     except Exception as e:
         unavailable(f"deepspeed.init_inference failed: {type(e).__name__}: {str(e)[:200]}")
@@ -130,7 +132,7 @@ def run_reference_arm(a) -> None:
         dist.all_reduce(stats, op=dist.ReduceOp.MAX)
     total_ms, dec_dev, dec_host, ttft_dev, ttft_host = stats.tolist()
     if rank == 0:
-        toks = a.steps * B * D
+        toks = a.steps * B * D * replicas
         print(json.dumps({
             "metric": "decode tokens/sec over restored multi-turn sessions (p50 restored-context TTFT in ttft_p50_ms)",
             "value": round(toks / (dec_dev / 1e3), 2), "unit": "tokens/s", "n_gpus": world, "steps": a.steps, "warmup": a.warmup,
@@ -139,8 +141,10 @@ def run_reference_arm(a) -> None:
             "ttft_p50_ms": round(ttft_dev, 3),
             "reference_path": "deepspeed.init_inference (v1, no kernel injection) over HF LlamaForCausalLM; context re-established "
                               "by recompute because the v2/HCache engine cannot run on sm_100 (see BASELINE.md §3)",
-            "config": {"model": a.model, "global_batch": B, "seq_len": ctx + n_new + D, "parallelism": f"tp{world}",
+            "config": {"model": a.model, "global_batch": B * replicas, "seq_len": ctx + n_new + D,
+                       "parallelism": f"tp{tp}" if replicas == 1 else f"dp{replicas}",
                        "restored_ctx": ctx, "new_turn_tokens": n_new, "decode_steps": D, "sessions_per_gpu": a.sessions},
             "e2e": {"value": round(toks / (dec_host / 1e3), 2), "unit": "tokens/s", "ttft_p50_ms": round(ttft_host, 3),
-                    "h2d_bytes_per_step": B * (ctx + n_new) * 8 * 2 + B * D * 8, "d2h_bytes_per_step": B * (D + 1) * 8},
+                    "h2d_bytes_per_step": (B * (ctx + n_new) * 8 * 2 + B * D * 8) * replicas,
+                    "d2h_bytes_per_step": B * (D + 1) * 8 * replicas},
         }), flush=True)

@@ -38,6 +38,10 @@ def parse():
     p.add_argument("--new-tokens", type=int, default=64, help="tokens of the new turn's prompt")
     p.add_argument("--decode-steps", type=int, default=32)
     p.add_argument("--sessions", type=int, default=8, help="concurrent sessions PER GPU (weak scaling: global batch = sessions x gpus)")
+    p.add_argument("--parallelism", default="dp", choices=["dp", "tp"],
+                   help="N > 1: 'dp' = one full replica per GPU serving its own sessions (a 7B model fits 13x in 180 GB; "
+                        "what a deployment does for throughput), 'tp' = one engine tensor-parallel over all GPUs (fused "
+                        "NVLink collectives, PCIe-sharded restore: lower TTFT, lower aggregate throughput)")
     p.add_argument("--plan", default="hidden", choices=["auto", "hidden"],
                    help="hidden: every layer from hidden states (fastest measured on 1xB200: 20.4 ms vs 21.6 ms); auto: planner mix with a recomputed prefix")
     return p.parse_args()
@@ -100,15 +104,17 @@ def run_ours(a):
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
         dist.init_process_group("nccl", device_id=dev)
     spec = named_arch(a.model)
-    B, ctx, n_new, D = a.sessions * world, a.ctx, a.new_tokens, a.decode_steps
+    tp = world if a.parallelism == "tp" else 1          # ranks that share one engine
+    replicas = world // tp                              # independent engines (data parallel)
+    B, ctx, n_new, D = a.sessions * tp, a.ctx, a.new_tokens, a.decode_steps   # sessions handled by THIS engine
     max_ctx = ctx + n_new + D + 64
     cfg = RaggedInferenceEngineConfig(
-        tensor_parallel={"tp_size": world},
+        tensor_parallel={"tp_size": tp},
         state_manager={"max_tracked_sequences": max(2 * B, 16), "max_ragged_batch_size": max(ctx, B * n_new) + 64,
                        "max_ragged_sequence_count": max(B, 8), "max_context": max_ctx,
                        "memory_config": {"mode": "allocate",
-                                         "size": int((B + 1) * (max_ctx + 128) * spec.kv_bytes_per_token_layer() * spec.n_layers / world)}},
-        hcache={"enabled": True, "capture": "off", "shard_capture": world > 1})
+                                         "size": int((B + 1) * (max_ctx + 128) * spec.kv_bytes_per_token_layer() * spec.n_layers / tp)}},
+        hcache={"enabled": True, "capture": "off", "shard_capture": tp > 1})
     eng = build_engine_from_arch(spec, cfg, seed=1234, dtype=torch.bfloat16, device=dev)
     model = eng.model()
     assert native.cuda_lib_loaded(), "sm_100a kernel library was not loaded"
@@ -134,14 +140,14 @@ def run_ours(a):
     torch.cuda.synchronize()
     eng.flush(10 ** 9)
     prefill_s = p0.elapsed_time(p1) / 1e3
-    plan = plan_restore(spec, ctx, LinkModel(tp_size=world), allow_kv=False, allow_recompute=(a.plan == "auto"),
+    plan = plan_restore(spec, ctx, LinkModel(tp_size=tp), allow_kv=False, allow_recompute=(a.plan == "auto"),
                         extra_compute_s=prefill_s)
     hidden_layers, recompute_layers = plan.layers_of("hidden"), plan.layers_of("none")
     lat_hidden = latents[hidden_layers[0]:] if hidden_layers else None  # the plan keeps a suffix of layers
     interleave = plan.interleave
     # tensor parallel: every rank keeps (and transfers) only its 1/tp row slice of the hidden states; the restore
     # kernels gather the slices from peer HBM over NVLink (needs the fused/symmetric-memory communicator)
-    sharded = world > 1 and bool(getattr(model.comm, "fused", False))
+    sharded = tp > 1 and bool(getattr(model.comm, "fused", False))
     if sharded:
         lo, hi = eng.latent_row_range(ctx)
         lat_slice = latents[:, lo:hi].contiguous().pin_memory()
@@ -210,11 +216,13 @@ def run_ours(a):
     total_ms = s_all.elapsed_time(e_all)
     stats = torch.tensor([total_ms, sum(rec["decode_dev_ms"]), sum(rec["decode_host_ms"]),
                           statistics.median(rec["ttft_dev_ms"]), statistics.median(rec["ttft_host_ms"])], device=dev)
+    launches = torch.tensor([float(kernels.launch_count - launches0)], device=dev)
     if world > 1:
-        dist.all_reduce(stats, op=dist.ReduceOp.MAX)
+        dist.all_reduce(stats, op=dist.ReduceOp.MAX)      # every time is the max over ranks
+        dist.all_reduce(launches, op=dist.ReduceOp.SUM)
     total_ms, dec_dev_ms, dec_host_ms, ttft_dev, ttft_host = stats.tolist()
     if rank == 0:
-        dec_tokens = a.steps * B * D
+        dec_tokens = a.steps * B * D * replicas           # whole job: every replica decodes its own sessions
         base_path = os.path.join(ROOT, "BASELINE.json")
         published = json.load(open(base_path)).get("published", {}) if os.path.exists(base_path) else {}
         ref_val = published.get("decode_tokens_per_sec")
@@ -226,17 +234,18 @@ def run_ours(a):
             "vs_baseline": (value / ref_val) if ref_val else None, "dtype": "bf16",
             "data": "synthetic tokens and hidden states, random-init weights", "impl": "ours",
             "ttft_p50_ms": round(ttft_dev, 3),
-            "config": {"model": a.model, "global_batch": B, "seq_len": ctx + n_new + D, "parallelism": f"tp{world}",
+            "config": {"model": a.model, "global_batch": B * replicas, "seq_len": ctx + n_new + D,
+                       "parallelism": f"tp{tp}" if replicas == 1 else f"dp{replicas}",
                        "restored_ctx": ctx, "new_turn_tokens": n_new, "decode_steps": D, "sessions_per_gpu": a.sessions,
                        "restore_plan": {"recompute_prefix_layers": 0 if sharded else len(recompute_layers),
                                         "hidden_state_layers": spec.n_layers if sharded else len(hidden_layers),
                                         "kv_offload_layers": 0, "tp_sharded_restore": sharded,
                                         "tp_collectives": "fused GEMM-epilogue reduction" if bool(getattr(model.comm, "fused", False))
-                                        else ("nccl" if world > 1 else "none")},
+                                        else ("nccl" if tp > 1 else "none")},
                        "l2_policy": f"working set per step (weights {model.w.n_bytes() / 2**30:.1f} GiB + KV) exceeds the 126 MB L2"},
             "e2e": {"value": round(dec_tokens / (dec_host_ms / 1e3), 2), "unit": "tokens/s", "ttft_p50_ms": round(ttft_host, 3),
-                    "h2d_bytes_per_step": h2d_step, "d2h_bytes_per_step": d2h_step},
-            "gpu_launches": kernels.launch_count - launches0,
+                    "h2d_bytes_per_step": h2d_step * replicas, "d2h_bytes_per_step": d2h_step * replicas},
+            "gpu_launches": int(launches.item()),
             "clocks": clocks,
         }
         print(json.dumps(out), flush=True)
