@@ -5,9 +5,14 @@
 //               paged cache through the block table (2-stage ring, SWIZZLE_128B)
 //   warp 1    : TMEM allocator + tcgen05.mma issuer:  S = Q K^T (K-major x K-major),
 //               O_tile = P V (P K-major from shared memory, V MN-major straight from its page layout)
-//   warps 2-5 : softmax — one thread per query row: tcgen05.ld S, causal mask, online max/sum in
-//               registers, P -> shared (UMMA K-major swizzled layout), then O += O_tile with the
-//               running rescale kept in registers (no TMEM read-modify-write)
+//   warps 2-9 : softmax — TWO threads per query row (warps w and w+4 share a TMEM lane quadrant and split the tile's
+//               128 key columns 64/64, exchanging only the row max through shared memory), so every scheduler has two
+//               warps to interleave: ONE tcgen05.ld pass pulls this thread's 64 scores into
+//               registers and releases S at once (so Q K^T of the next tile runs under this tile's exponentials),
+//               causal mask, online max/sum, P -> shared (UMMA K-major swizzled layout).
+//   O accumulates in TMEM across all KV tiles (PV issued with accumulate); it is rescaled in place only when a
+//   row's running max grows by more than 2^8 (lazy rescale: probabilities are computed against a slightly stale
+//   max, which is exact after the final division by the matching row sum)
 //
 // Stands in for the external paged flash kernel of the reference
 // (deepspeed/inference/v2/kernels/ragged_ops/blocked_flash/blocked_flash.cpp:21-101; atoms:
@@ -18,7 +23,7 @@
 
 namespace hds {
 
-constexpr int kPfThreads = 192;
+constexpr int kPfThreads = 320;   // TMA warp + MMA warp + 8 softmax warps (two per TMEM lane quadrant)
 constexpr int kPfTok = 128;
 constexpr int kPfStages = 2;
 
@@ -30,7 +35,7 @@ struct PrefillArgs {
     int n_q_heads, n_kv_heads, block_size;
     float scale_log2;
     int n_splits;       // KV range split over gridDim.z CTAs
-    int32_t* tickets;   // [n_items][n_q_heads][4]  (one per 32-row quadrant), zero between calls
+    int32_t* tickets;   // [n_items][n_q_heads][4 quadrants][2 halves], zero between calls
     float* ws_ml;       // [n_items][n_q_heads][n_splits][128][2]
     float* ws_o;        // [n_items][n_q_heads][n_splits][128][D]
 };
@@ -45,7 +50,7 @@ template <int D>
 __host__ __device__ constexpr size_t pf_smem_bytes() {
     // Q [128 x D] + P [128 x 128] + stages x (K + V) [128 x D] (16-bit) + barriers + alignment slack
     return static_cast<size_t>(128) * D * 2 + 128 * 128 * 2 + static_cast<size_t>(kPfStages) * 2 * kPfTok * D * 2 + 256 +
-           1024;
+           2 * 2 * 128 * 4 /*row-max exchange*/ + 1024;
 }
 
 template <int D, bool kBf16>
@@ -70,12 +75,17 @@ paged_attn_prefill_kernel(const __grid_constant__ CUtensorMap tmap_q, const __gr
     uint64_t* kv_empty = kv_full + kPfStages;
     uint64_t* s_full = kv_empty + kPfStages;
     uint64_t* p_full = s_full + 1;
-    uint64_t* o_full = p_full + 1;
-    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(o_full + 1);
+    uint64_t* o_full = p_full + 1;   // PV of a tile has completed: O is stable, the P buffer is free
+    uint64_t* s_empty = o_full + 1;  // all four softmax warps hold S in registers: the S accumulator is free
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(s_empty + 1);
+    float* xch = reinterpret_cast<float*>(tmem_slot + 2);  // [2 (tile parity)][2 (half)][128 rows] row-max exchange
 
     const uint32_t warp = warp_id(), lane = lane_id();
     pdl_enter();  // PDL: the next kernel may be scheduled; this one needs its predecessor's Q and KV writes
-    const hds_attn_item item = a.items[blockIdx.x];
+    // heaviest work first: the host lists a sequence's query tiles in position order, so later items see more keys;
+    // walking them backwards leaves the short ones to fill the tail of the schedule
+    const int item_idx = static_cast<int>(gridDim.x - 1 - blockIdx.x);
+    const hds_attn_item item = a.items[item_idx];
     const int head = blockIdx.y;
     const int kvh = head / (a.n_q_heads / a.n_kv_heads);
     const int kv_len = item.pos0 + item.n_q;
@@ -98,8 +108,9 @@ paged_attn_prefill_kernel(const __grid_constant__ CUtensorMap tmap_q, const __gr
             mbar_init(&kv_empty[i], 1);
         }
         mbar_init(s_full, 1);
-        mbar_init(p_full, 4);
+        mbar_init(p_full, 8);
         mbar_init(o_full, 1);
+        mbar_init(s_empty, 8);
         fence_barrier_init();
     }
     if (warp == 1) {
@@ -170,7 +181,16 @@ paged_attn_prefill_kernel(const __grid_constant__ CUtensorMap tmap_q, const __gr
             issue_qk(0);
             uint32_t stage = 0, phase = 0;
             for (int ti = 0; ti < n_tiles; ++ti) {
-                // ---- O_tile = P V for tile ti ----
+                // ---- S for tile ti+1 as soon as the softmax warps have pulled S(ti) into registers ----
+                const uint32_t nstage = (stage + 1 == kPfStages) ? 0 : stage + 1;
+                const uint32_t nphase = (stage + 1 == kPfStages) ? phase ^ 1 : phase;
+                if (ti + 1 < n_tiles) {
+                    mbar_wait(s_empty, ti & 1);
+                    mbar_wait(&kv_full[nstage], nphase);
+                    tc_fence_after();
+                    issue_qk(nstage);
+                }
+                // ---- O += P V for tile ti ----
                 mbar_wait(p_full, ti & 1);
                 tc_fence_after();
                 const uint8_t* vtile = kv_sm + stage * 2 * TILE_BYTES + TILE_BYTES;
@@ -181,126 +201,135 @@ paged_attn_prefill_kernel(const __grid_constant__ CUtensorMap tmap_q, const __gr
                         make_desc_kmajor_sw128(smem_u32(p_sm + (kk >> 2) * PANEL_BYTES)) + 2 * (kk & 3);
                     // B = V: MN-major; 16 tokens = 16 rows of 128 B; panels of 64 dims are PANEL_BYTES apart
                     const uint64_t dv = make_desc_mnmajor_sw128(smem_u32(vtile + kk * 16 * 128), PANEL_BYTES);
-                    umma_f16_ss(tmem_o, dp, dv, IDESC_PV, kk > 0 ? 1u : 0u);
+                    umma_f16_ss(tmem_o, dp, dv, IDESC_PV, (ti > 0 || kk > 0) ? 1u : 0u);
                 }
                 umma_commit(o_full);
                 umma_commit(&kv_empty[stage]);
-                if (++stage == kPfStages) {
-                    stage = 0;
-                    phase ^= 1;
-                }
-                // ---- S for tile ti+1 overlaps the softmax threads' O merge ----
-                if (ti + 1 < n_tiles) {
-                    mbar_wait(&kv_full[stage], phase);
-                    tc_fence_after();
-                    issue_qk(stage);
-                }
+                stage = nstage;
+                phase = nphase;
             }
         }
     } else {
         // ===================== softmax / output (warps 2..5, one thread per query row) =====================
-        const uint32_t quad = warp & 3;
-        const int r = quad * 32 + lane;  // query row inside the item
+        const uint32_t quad = warp & 3;              // TMEM lane quadrant this warp may touch
+        const uint32_t half = (warp - 2) >> 2;       // which 64 key columns (and which half of the output dims)
+        const int r = quad * 32 + lane;              // query row inside the item
         const int q_pos = item.pos0 + r;
         const uint32_t lane_addr = (quad * 32u) << 16;
-        float o_acc[D];
-#pragma unroll
-        for (int i = 0; i < D; ++i) o_acc[i] = 0.0f;
-        float m_run = -INFINITY, l_run = 0.0f;
-        uint8_t* p_row = p_sm + r * 128;
+        constexpr int HC = kPfTok / 2;               // key columns per thread
+        constexpr int HD2 = D / 2;                   // output dims per thread
+        float m_run = -INFINITY, l_run = 0.0f;       // l_run: this thread's columns only
+        uint8_t* p_row = p_sm + half * PANEL_BYTES + r * 128;   // half h owns P panel h (64 tokens = 128 B per row)
+        constexpr float kRescaleThreshold = 8.0f;    // log2 units: probabilities stay below 2^8 against a stale max
+        auto pair_sync = [&]() { asm volatile("bar.sync %0, 64;" ::"r"(1 + quad) : "memory"); };
         for (int ti = 0; ti < n_tiles; ++ti) {
-            const int tok0 = (t0 + ti) * kPfTok;
-            // every key of this tile is visible to every query row unless the tile reaches past the
-            // first query position (rows only move the causal frontier forward) — warp-uniform
-            const bool need_mask = tok0 + kPfTok - 1 > item.pos0;
+            const int tok0 = (t0 + ti) * kPfTok + half * HC;
+            const bool need_mask = (t0 + ti) * kPfTok + kPfTok - 1 > item.pos0;  // warp-uniform
             mbar_wait(s_full, ti & 1);
             tc_fence_after();
-            // pass 1: row max
+            // ---- my 64 scores -> registers, then hand the S accumulator back to the MMA warp ----
+            uint32_t sr[HC];
+#pragma unroll
+            for (int c = 0; c < HC; c += 32)
+                tmem_ld_32x32(tmem_s + lane_addr + half * HC + c, *reinterpret_cast<uint32_t(*)[32]>(&sr[c]));
+            tmem_ld_wait();
+            tc_fence_before();
+            __syncwarp();
+            if (lane == 0) mbar_arrive(s_empty);
             float tmax = -INFINITY;
-#pragma unroll 1
-            for (int c = 0; c < kPfTok; c += 32) {
-                uint32_t sr[32];
-                tmem_ld_32x32(tmem_s + lane_addr + c, sr);
-                tmem_ld_wait();
-                if (need_mask) {
+            if (need_mask) {
 #pragma unroll
-                    for (int j = 0; j < 32; ++j) {
-                        const int kv_pos = tok0 + c + j;
-                        const float sv = (kv_pos <= q_pos && kv_pos < kv_len) ? __uint_as_float(sr[j]) : -INFINITY;
-                        tmax = fmaxf(tmax, sv);
-                    }
-                } else {
-#pragma unroll
-                    for (int j = 0; j < 32; ++j) tmax = fmaxf(tmax, __uint_as_float(sr[j]));
+                for (int j = 0; j < HC; ++j) {
+                    const int kv_pos = tok0 + j;
+                    const float sv = (kv_pos <= q_pos && kv_pos < kv_len) ? __uint_as_float(sr[j]) : -INFINITY;
+                    sr[j] = __float_as_uint(sv);
+                    tmax = fmaxf(tmax, sv);
                 }
+            } else {
+#pragma unroll
+                for (int j = 0; j < HC; ++j) tmax = fmaxf(tmax, __uint_as_float(sr[j]));
             }
-            const float m_new = fmaxf(m_run, tmax * a.scale_log2);
-            const float alpha = (m_run == -INFINITY) ? 0.0f : ex2_approx(m_run - m_new);
+            // row max over both halves
+            float* x = xch + (ti & 1) * 256;
+            x[half * 128 + r] = tmax;
+            pair_sync();
+            tmax = fmaxf(tmax, x[(half ^ 1) * 128 + r]);
+            // lazy rescale: move the reference max only when it grew by more than the threshold
+            const float m_cand = fmaxf(m_run, tmax * a.scale_log2);
+            const bool grow = (m_cand > m_run + kRescaleThreshold) || (m_run == -INFINITY && m_cand != -INFINITY);
+            const float m_new = grow ? m_cand : m_run;
+            const float alpha = (!grow || m_run == -INFINITY) ? (grow ? 0.0f : 1.0f) : ex2_approx(m_run - m_new);
             const float m_sub = (m_new == -INFINITY) ? 0.0f : m_new;  // fully masked row: exp2(-inf - 0) = 0
-            // pass 2: probabilities -> shared memory (A operand of the PV MMA)
-            float psum = 0.0f;
-#pragma unroll 1
-            for (int c = 0; c < kPfTok; c += 32) {
-                uint32_t sr[32];
-                tmem_ld_32x32(tmem_s + lane_addr + c, sr);
-                tmem_ld_wait();
-                uint32_t packed[16];
-                if (need_mask) {
+            float ps0 = 0.0f, ps1 = 0.0f;
+            uint32_t packed[HC / 2];
 #pragma unroll
-                    for (int j = 0; j < 32; j += 2) {
-                        const int kv0 = tok0 + c + j;
-                        const float s0 = (kv0 <= q_pos && kv0 < kv_len) ? __uint_as_float(sr[j]) : -INFINITY;
-                        const float s1 = (kv0 + 1 <= q_pos && kv0 + 1 < kv_len) ? __uint_as_float(sr[j + 1]) : -INFINITY;
-                        const float p0 = ex2_approx(fmaf(s0, a.scale_log2, -m_sub));
-                        const float p1 = ex2_approx(fmaf(s1, a.scale_log2, -m_sub));
-                        psum += p0 + p1;
-                        packed[j >> 1] = pack2<kBf16>(p0, p1);
+            for (int j = 0; j < HC; j += 2) {
+                const float p0 = ex2_approx(fmaf(__uint_as_float(sr[j]), a.scale_log2, -m_sub));
+                const float p1 = ex2_approx(fmaf(__uint_as_float(sr[j + 1]), a.scale_log2, -m_sub));
+                ps0 += p0;
+                ps1 += p1;
+                packed[j >> 1] = pack2<kBf16>(p0, p1);
+            }
+            l_run = l_run * alpha + (ps0 + ps1);
+            m_run = m_new;
+            // PV of the previous tile must be complete before P is overwritten or O is rescaled
+            if (ti > 0) {
+                mbar_wait(o_full, (ti - 1) & 1);
+                tc_fence_after();
+                const bool rescale = grow && alpha != 0.0f;  // alpha == 0: nothing accumulated for this row yet
+                if (__any_sync(0xffffffffu, rescale)) {
+                    const float f = rescale ? alpha : 1.0f;
+#pragma unroll
+                    for (int c = 0; c < HD2; c += 32) {
+                        uint32_t orr[32];
+                        tmem_ld_32x32(tmem_o + lane_addr + half * HD2 + c, orr);
+                        tmem_ld_wait();
+#pragma unroll
+                        for (int j = 0; j < 32; ++j) orr[j] = __float_as_uint(__uint_as_float(orr[j]) * f);
+                        tmem_st_32x32(tmem_o + lane_addr + half * HD2 + c, orr);
                     }
-                } else {
-#pragma unroll
-                    for (int j = 0; j < 32; j += 2) {
-                        const float p0 = ex2_approx(fmaf(__uint_as_float(sr[j]), a.scale_log2, -m_sub));
-                        const float p1 = ex2_approx(fmaf(__uint_as_float(sr[j + 1]), a.scale_log2, -m_sub));
-                        psum += p0 + p1;
-                        packed[j >> 1] = pack2<kBf16>(p0, p1);
-                    }
-                }
-                // 32 tokens = 4 chunks of 16 B in panel c/64, swizzled by (row & 7)
-                uint8_t* prow_panel = p_row + (c >> 6) * PANEL_BYTES;
-#pragma unroll
-                for (int q4 = 0; q4 < 4; ++q4) {
-                    const int chunk = ((c & 63) >> 3) + q4;
-                    uint4 v = make_uint4(packed[4 * q4], packed[4 * q4 + 1], packed[4 * q4 + 2], packed[4 * q4 + 3]);
-                    *reinterpret_cast<uint4*>(prow_panel + ((chunk ^ (r & 7)) << 4)) = v;
+                    tmem_st_wait();
                 }
             }
-            l_run = l_run * alpha + psum;
-            m_run = m_new;
-            // make P visible to the tensor core (async proxy), then signal the MMA warp
+            // probabilities -> shared memory (A operand of the PV MMA): 8 tokens per 16-byte chunk, swizzled by row
+#pragma unroll
+            for (int ch = 0; ch < HC / 8; ++ch) {
+                const uint4 v = make_uint4(packed[4 * ch], packed[4 * ch + 1], packed[4 * ch + 2], packed[4 * ch + 3]);
+                *reinterpret_cast<uint4*>(p_row + ((ch ^ (r & 7)) << 4)) = v;
+            }
+            // make P (and a rescaled O) visible to the tensor core, then signal the MMA warp
             tc_fence_before();
             fence_proxy_async_smem();
             __syncwarp();
             if (lane == 0) mbar_arrive(p_full);
-            // merge O_tile
-            mbar_wait(o_full, ti & 1);
-            tc_fence_after();
-#pragma unroll
-            for (int c = 0; c < D; c += 32) {
-                uint32_t orr[32];
-                tmem_ld_32x32(tmem_o + lane_addr + c, orr);
-                tmem_ld_wait();
-#pragma unroll
-                for (int j = 0; j < 32; ++j) o_acc[c + j] = fmaf(o_acc[c + j], alpha, __uint_as_float(orr[j]));
-            }
-            tc_fence_before();
         }
+        // ---- total row sum over both halves, then my half of the final O row from TMEM ----
+        {
+            float* x = xch + (n_tiles & 1) * 256;
+            x[half * 128 + r] = l_run;
+            pair_sync();
+            l_run += x[(half ^ 1) * 128 + r];
+        }
+        mbar_wait(o_full, (n_tiles - 1) & 1);
+        tc_fence_after();
+        float o_acc[HD2];
+#pragma unroll
+        for (int c = 0; c < HD2; c += 32) {
+            uint32_t orr[32];
+            tmem_ld_32x32(tmem_o + lane_addr + half * HD2 + c, orr);
+            tmem_ld_wait();
+#pragma unroll
+            for (int j = 0; j < 32; ++j) o_acc[c + j] = __uint_as_float(orr[j]);
+        }
+        tc_fence_before();
         const bool row_valid = r < item.n_q;
-        char* dst = reinterpret_cast<char*>(a.out) + (static_cast<int64_t>(item.q_row0 + r) * a.n_q_heads + head) * D * 2;
+        char* dst = reinterpret_cast<char*>(a.out) +
+                    ((static_cast<int64_t>(item.q_row0 + r) * a.n_q_heads + head) * D + half * HD2) * 2;
         if (eff_splits == 1) {
             if (row_valid) {
                 const float inv = 1.0f / l_run;
 #pragma unroll
-                for (int c = 0; c < D; c += 8) {
+                for (int c = 0; c < HD2; c += 8) {
                     uint4 v;
                     v.x = pack2<kBf16>(o_acc[c + 0] * inv, o_acc[c + 1] * inv);
                     v.y = pack2<kBf16>(o_acc[c + 2] * inv, o_acc[c + 3] * inv);
@@ -310,19 +339,19 @@ paged_attn_prefill_kernel(const __grid_constant__ CUtensorMap tmap_q, const __gr
                 }
             }
         } else if (static_cast<int>(quad * 32) < item.n_q) {  // warp-uniform: this quadrant owns valid rows
-            // ---- split-KV: park the partial (O, m, l); the last split of this quadrant merges ----
-            const int64_t unit = static_cast<int64_t>(blockIdx.x) * a.n_q_heads + head;
+            // ---- split-KV: park the partial (O, m, l); the last split of this (quadrant, half) merges its dims ----
+            const int64_t unit = static_cast<int64_t>(item_idx) * a.n_q_heads + head;
             const int64_t ws_row = (unit * a.n_splits + split) * 128 + r;
             if (row_valid) {
-                float4* wo = reinterpret_cast<float4*>(a.ws_o + ws_row * D);
+                float4* wo = reinterpret_cast<float4*>(a.ws_o + ws_row * D + half * HD2);
 #pragma unroll
-                for (int c = 0; c < D; c += 4) __stcg(wo + (c >> 2), make_float4(o_acc[c], o_acc[c + 1], o_acc[c + 2], o_acc[c + 3]));
-                __stcg(reinterpret_cast<float2*>(a.ws_ml + ws_row * 2), make_float2(m_run, l_run));
+                for (int c = 0; c < HD2; c += 4) __stcg(wo + (c >> 2), make_float4(o_acc[c], o_acc[c + 1], o_acc[c + 2], o_acc[c + 3]));
+                if (half == 0) __stcg(reinterpret_cast<float2*>(a.ws_ml + ws_row * 2), make_float2(m_run, l_run));
             }
             __threadfence();
-            __syncwarp();
+            pair_sync();  // both halves of the rows (O dims and (m, l)) are published before either takes a ticket
             int last = 0;
-            if (lane == 0) last = (atomicAdd(&a.tickets[unit * 4 + quad], 1) == eff_splits - 1) ? 1 : 0;
+            if (lane == 0) last = (atomicAdd(&a.tickets[(unit * 4 + quad) * 2 + half], 1) == eff_splits - 1) ? 1 : 0;
             last = __shfl_sync(0xffffffffu, last, 0);
             if (last) {
                 __threadfence();
@@ -332,15 +361,15 @@ paged_attn_prefill_kernel(const __grid_constant__ CUtensorMap tmap_q, const __gr
                         mx = fmaxf(mx, __ldcg(a.ws_ml + ((unit * a.n_splits + sp) * 128 + r) * 2));
                     float l_tot = 0.0f;
 #pragma unroll
-                    for (int i = 0; i < D; ++i) o_acc[i] = 0.0f;
+                    for (int i = 0; i < HD2; ++i) o_acc[i] = 0.0f;
                     for (int sp = 0; sp < eff_splits; ++sp) {
                         const int64_t row_sp = (unit * a.n_splits + sp) * 128 + r;
                         const float2 ml = __ldcg(reinterpret_cast<const float2*>(a.ws_ml + row_sp * 2));
                         const float w = (ml.x == -INFINITY) ? 0.0f : ex2_approx(ml.x - mx);
                         l_tot = fmaf(w, ml.y, l_tot);
-                        const float4* wo = reinterpret_cast<const float4*>(a.ws_o + row_sp * D);
+                        const float4* wo = reinterpret_cast<const float4*>(a.ws_o + row_sp * D + half * HD2);
 #pragma unroll
-                        for (int c = 0; c < D; c += 4) {
+                        for (int c = 0; c < HD2; c += 4) {
                             const float4 t = __ldcg(wo + (c >> 2));
                             o_acc[c] = fmaf(w, t.x, o_acc[c]);
                             o_acc[c + 1] = fmaf(w, t.y, o_acc[c + 1]);
@@ -350,7 +379,7 @@ paged_attn_prefill_kernel(const __grid_constant__ CUtensorMap tmap_q, const __gr
                     }
                     const float inv = 1.0f / l_tot;
 #pragma unroll
-                    for (int c = 0; c < D; c += 8) {
+                    for (int c = 0; c < HD2; c += 8) {
                         uint4 v;
                         v.x = pack2<kBf16>(o_acc[c + 0] * inv, o_acc[c + 1] * inv);
                         v.y = pack2<kBf16>(o_acc[c + 2] * inv, o_acc[c + 3] * inv);
@@ -360,7 +389,7 @@ paged_attn_prefill_kernel(const __grid_constant__ CUtensorMap tmap_q, const __gr
                     }
                 }
                 __syncwarp();
-                if (lane == 0) a.tickets[unit * 4 + quad] = 0;
+                if (lane == 0) a.tickets[(unit * 4 + quad) * 2 + half] = 0;
             }
         }
     }
@@ -399,7 +428,7 @@ static inline int64_t pf_align256(int64_t x) { return (x + 255) & ~int64_t(255);
 extern "C" int64_t hds_paged_attention_prefill_workspace_bytes(int n_items, int n_q_heads, int head_dim, int n_splits) {
     if (n_splits <= 1) return 0;
     const int64_t units = static_cast<int64_t>(n_items) * n_q_heads;
-    return pf_align256(units * 4 * 4) + pf_align256(units * n_splits * 128 * 2 * 4) +
+    return pf_align256(units * 8 * 4) + pf_align256(units * n_splits * 128 * 2 * 4) +
            pf_align256(units * n_splits * 128 * head_dim * 4);
 }
 
@@ -433,8 +462,8 @@ extern "C" int hds_paged_attention_prefill(const void* q, void* out, const void*
         const int64_t units = static_cast<int64_t>(n_items) * n_q_heads;
         char* ws = reinterpret_cast<char*>(workspace);
         a.tickets = reinterpret_cast<int32_t*>(ws);
-        a.ws_ml = reinterpret_cast<float*>(ws + pf_align256(units * 4 * 4));
-        a.ws_o = reinterpret_cast<float*>(ws + pf_align256(units * 4 * 4) + pf_align256(units * n_splits * 128 * 2 * 4));
+        a.ws_ml = reinterpret_cast<float*>(ws + pf_align256(units * 8 * 4));
+        a.ws_o = reinterpret_cast<float*>(ws + pf_align256(units * 8 * 4) + pf_align256(units * n_splits * 128 * 2 * 4));
     }
     CUtensorMap tq, tkv;
     int rc = make_tmap_2d_16b(&tq, q, static_cast<uint64_t>(n_q_heads) * head_dim, static_cast<uint64_t>(n_q_rows),

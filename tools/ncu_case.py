@@ -1,5 +1,5 @@
 """Runs ONE kernel case a handful of times so that ncu can capture it (see B200_PROFILING.md).
-usage: python tools/ncu_case.py <prefill|decode_gemm|restore|attn_decode|gemm>"""
+usage: python tools/ncu_case.py <prefill|prefill_full|decode_gemm|restore|attn_decode|gemm>"""
 import math
 import os
 import sys
@@ -28,6 +28,15 @@ if case == "prefill":
     q = rand(n_new, nq, d)
     out = torch.empty_like(q)
     fn = lambda: K.paged_attention_prefill(q, out, cache, tables, items, 1, nq, nkv, d, bs, 1 / math.sqrt(d))
+elif case == "prefill_full":
+    d, bs, nq, nkv, n_new = 128, 64, 32, 32, 4096
+    nb = (n_new + bs - 1) // bs
+    cache = (torch.randn(nb, 2, nkv, bs, d, device=dev) * 0.3).to(torch.bfloat16)
+    tables = torch.arange(nb, device=dev, dtype=torch.int32).view(1, nb)
+    items = torch.tensor([(0, r0, 128, r0) for r0 in range(0, n_new, 128)], dtype=torch.int32, device=dev)
+    q = rand(n_new, nq, d)
+    out = torch.empty_like(q)
+    fn = lambda: K.paged_attention_prefill(q, out, cache, tables, items, items.shape[0], nq, nkv, d, bs, 1 / math.sqrt(d))
 elif case == "decode_gemm":
     M, N, Kd = 16, 12288, 4096
     a, w = rand(M, Kd), rand(N, Kd, scale=Kd ** -0.5)
