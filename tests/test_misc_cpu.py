@@ -192,3 +192,24 @@ def test_curriculum_sampler_and_random_ltd():
     x = torch.randn(2, 16, 8)
     y = layer(x)
     assert y.shape == x.shape and int((y == x).all(-1).sum()) == 2 * 12      # 12 of 16 tokens per sample skipped the layer
+
+
+def test_multinode_runner_commands():
+    from hcache_deepspeed_b200.launcher.multinode_runner import RUNNERS
+    args = types.SimpleNamespace(user_script="train.py", user_args=["--x", "1"], master_addr="10.0.0.1", master_port=29500,
+                                 hostfile="/job/hostfile", launcher_args="", include="", exclude="", num_nodes=-1, num_gpus=-1,
+                                 no_python=False, module=False, comment="")
+    res = {"n1": [0, 1], "n2": [0, 1]}
+    cmds = {}
+    for name, cls in RUNNERS.items():
+        r = cls(args, "QUJD")
+        r.add_export("NCCL_DEBUG", "INFO")
+        cmds[name] = r.get_cmd({}, res)
+    assert cmds["pdsh"][:2] == ["pdsh", "-S"] and "n1,n2" in cmds["pdsh"] and "--node_rank=%n" in cmds["pdsh"]
+    assert cmds["openmpi"][:3] == ["mpirun", "-n", "4"] and "NCCL_DEBUG=INFO" in cmds["openmpi"]
+    i = cmds["mpich"].index("-genv")
+    assert cmds["mpich"][i:i + 3] == ["-genv", "NCCL_DEBUG", "INFO"] and cmds["mpich"][3:5] == ["-ppn", "2"]
+    assert cmds["impi"][1:3] == ["-hosts", "n1,n2"] and cmds["slurm"][0] == "srun" and "--export=ALL,NCCL_DEBUG=INFO" in cmds["slurm"]
+    assert cmds["mvapich"][-3:] == ["train.py", "--x", "1"]
+    with pytest.raises(ValueError):
+        RUNNERS["mpich"](args, "x").get_cmd({}, {"a": [0], "b": [0, 1]})
