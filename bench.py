@@ -100,6 +100,8 @@ def run_ours(a):
     local = int(os.environ.get("LOCAL_RANK", 0))
     torch.cuda.set_device(local)
     dev = torch.device("cuda", local)
+    from hcache_deepspeed_b200.utils.numa import bind_to_gpu_numa
+    numa_cpus = bind_to_gpu_numa(local)   # pinned hidden-state buffers land on the GPU's own NUMA node
     if world > 1:
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
         dist.init_process_group("nccl", device_id=dev)
@@ -237,6 +239,7 @@ def run_ours(a):
             "config": {"model": a.model, "global_batch": B * replicas, "seq_len": ctx + n_new + D,
                        "parallelism": f"tp{tp}" if replicas == 1 else f"dp{replicas}",
                        "restored_ctx": ctx, "new_turn_tokens": n_new, "decode_steps": D, "sessions_per_gpu": a.sessions,
+                       "numa_bound_cpus": len(numa_cpus),
                        "restore_plan": {"recompute_prefix_layers": 0 if sharded else len(recompute_layers),
                                         "hidden_state_layers": spec.n_layers if sharded else len(hidden_layers),
                                         "kv_offload_layers": 0, "tp_sharded_restore": sharded,

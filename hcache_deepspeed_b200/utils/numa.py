@@ -51,3 +51,23 @@ def get_numactl_cmd(bind_core_list: Optional[str], num_local_procs: int, local_r
         cmd += ["-m", str(owning[0])]
     cmd += ["-C", ",".join(map(str, mine))]
     return per, cmd
+
+
+def bind_to_gpu_numa(gpu_index: int) -> List[int]:
+    """Pin this process to the CPUs that are local to ``gpu_index`` (NVML's CPU affinity mask), so pinned host buffers
+    it allocates afterwards are first-touched on the GPU's own NUMA node: with 8 ranks streaming hidden states at once
+    the host links only reach their rate when every copy reads node-local memory. Returns the CPU list ([] if NVML or
+    the affinity call is unavailable; the process is left untouched then)."""
+    try:
+        import pynvml
+        pynvml.nvmlInit()
+        h = pynvml.nvmlDeviceGetHandleByIndex(gpu_index)
+        n_words = (os.cpu_count() + 63) // 64
+        mask = pynvml.nvmlDeviceGetCpuAffinity(h, n_words)
+        cpus = [w * 64 + b for w, word in enumerate(mask) for b in range(64) if (word >> b) & 1]
+        cpus = [c for c in cpus if c in os.sched_getaffinity(0)]
+        if cpus:
+            os.sched_setaffinity(0, cpus)
+        return cpus
+    except Exception:
+        return []
