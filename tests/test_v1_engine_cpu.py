@@ -92,3 +92,32 @@ def test_injected_generate_greedy_matches_hf():
     got = eng.generate(input_ids=ids, max_new_tokens=8, do_sample=False)
     want = hf.generate(input_ids=ids, max_new_tokens=8, do_sample=False, pad_token_id=0)
     assert torch.equal(got[:, :20], want[:, :20])
+
+
+def test_v1_fused_layer_incremental_decode_matches_full_forward():
+    """DeepSpeedTransformerInference with its contiguous KV cache: prompt + token-by-token decode equals one full pass."""
+    from hcache_deepspeed_b200.model_implementations import DeepSpeedTransformerInference
+    from hcache_deepspeed_b200.ops.transformer.inference import DeepSpeedInferenceConfig
+    DeepSpeedTransformerInference.release()
+    torch.manual_seed(0)
+    cfg = DeepSpeedInferenceConfig(hidden_size=32, heads=4, num_hidden_layers=1, dtype=torch.float32, pre_layer_norm=True,
+                                   rotary_dim=8, rotate_half=True, rotate_every_two=False, mlp_act_func_type="gelu",
+                                   max_out_tokens=32, layer_norm_eps=1e-5)
+    layer = DeepSpeedTransformerInference(cfg).eval()
+    for p in layer.parameters():
+        if p.dim() > 1:
+            p.data.normal_(0, 0.1)
+    x = torch.randn(2, 7, 32)
+    full = layer(x)[0]
+    DeepSpeedTransformerInference.reset_cache()
+    out_p, present = layer(x[:, :5], use_cache=True)
+    assert present[0].shape == (2, 4, 5, 8)
+    outs = [out_p]
+    for t in (5, 6):
+        outs.append(layer(x[:, t:t + 1], layer_past=present, use_cache=True)[0])
+    torch.testing.assert_close(torch.cat(outs, dim=1), full, rtol=1e-4, atol=1e-5)
+    # reference formula for the first token (no attention context beyond itself)
+    ops = layer.mlp.ops
+    q_k = ops.apply_rotary_pos_emb(torch.randn(1, 2, 3, 8), torch.randn(1, 2, 3, 8), 8, 0, 2, True)
+    assert q_k[0].shape == (1, 2, 3, 8)
+    DeepSpeedTransformerInference.release()
