@@ -26,7 +26,8 @@ class DeepSpeedTPConfig(DeepSpeedConfigModel):
 class QuantizationConfig(DeepSpeedConfigModel):
     quantization_mode: Optional[str] = None
     """Weight quantization mode. The reference's only mode ('wf6af16') is Ampere-only
-    (``modules/heuristics.py:93-104``); accepted values here: None."""
+    (``modules/heuristics.py:93-104``); accepted values here: None, or 'wf8af8' (E4M3 weights per output channel
+    and activations per token on the fp8 tensor cores — ``modules/implementations.py::Fp8TensorCoreLinear``)."""
 
 
 class HCacheConfig(DeepSpeedConfigModel):

@@ -81,6 +81,49 @@ class BlasFPLinear(DSLinearBase):
         return ops.gemm(hidden_states, w, out, bias=b, act=self.act, gated=self.gated)
 
 
+@DSLinearRegistry.register_module
+class Fp8TensorCoreLinear(BlasFPLinear):
+    """W8A8 linear on the fp8 tensor cores (``quantization_mode = "wf8af8"``): weights are quantised to E4M3 per output
+    channel once (``transform_param``), activations per token on every call; the GEMM is ``tcgen05.mma.kind::f8f6f4``
+    with both scales applied in the epilogue (``ops/csrc/gemm_fp8.cu``). Takes the place of the reference's
+    ``quantized_wf6af16_linear`` (``implementations/linear/quantized_linear.py:24-205``), whose kernel is sm_80-only."""
+
+    @staticmethod
+    def name():
+        return "fp8_tcgen05_linear"
+
+    @staticmethod
+    def supports_config(config: DSLinearConfig) -> bool:
+        return BlasFPLinear.supports_config(config) and config.in_channels % 16 == 0
+
+    def transform_param(self, param: torch.Tensor) -> torch.Tensor:
+        param = super().transform_param(param)
+        if param.dim() != 2:
+            return param  # biases stay in the activation dtype
+        if param.is_cuda:
+            from ....ops import kernels as K
+            q, scales = K.quantize_fp8_rows(param.contiguous())
+        else:
+            amax = param.float().abs().amax(dim=1)
+            scales = torch.where(amax > 0, amax / 448.0, torch.ones_like(amax))
+            q = (param.float() / scales[:, None]).to(torch.float8_e4m3fn).view(torch.uint8)
+        q.scales = scales
+        return q
+
+    def forward(self, hidden_states: torch.Tensor, w: torch.Tensor, b: Optional[torch.Tensor] = None) -> torch.Tensor:
+        n_out = w.shape[0] // 2 if self.gated else w.shape[0]
+        if hidden_states.is_cuda:
+            from ....ops import kernels as K
+            out = torch.empty((hidden_states.shape[0], n_out), dtype=hidden_states.dtype, device=hidden_states.device)
+            aq, a_s = K.quantize_fp8_rows(hidden_states)
+            return K.gemm_fp8(aq, a_s, w, w.scales, out, bias=b, act=self.act, gated=self.gated)
+        amax = hidden_states.float().abs().amax(dim=1, keepdim=True)
+        a_s = torch.where(amax > 0, amax / 448.0, torch.ones_like(amax))
+        ad = (hidden_states.float() / a_s).to(torch.float8_e4m3fn).float() * a_s
+        wd = w.view(torch.float8_e4m3fn).float() * w.scales[:, None]
+        return ref.gemm(ad, wd, bias=b, act=self.act, gated=self.gated, out_dtype=hidden_states.dtype)
+
+
 class _PreNorm(DSPreNormBase):
     layer_norm = False
 

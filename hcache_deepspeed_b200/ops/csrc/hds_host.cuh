@@ -123,6 +123,32 @@ inline int make_tmap_2d_16b(CUtensorMap* map, const void* base, uint64_t inner, 
     return HDS_OK;
 }
 
+// 2D tensor of 8-bit elements (fp8 operands): box_inner is in BYTES (= elements), 128 for SWIZZLE_128B
+inline int make_tmap_2d_8b(CUtensorMap* map, const void* base, uint64_t inner, uint64_t outer, uint64_t pitch_bytes,
+                           uint32_t box_inner, uint32_t box_outer) {
+    auto enc = tensor_map_encoder();
+    if (!enc) {
+        set_error("cuTensorMapEncodeTiled unavailable (no CUDA driver?)");
+        return HDS_ERR_DRIVER;
+    }
+    if ((reinterpret_cast<uintptr_t>(base) & 15) || (pitch_bytes & 15)) {
+        set_error("TMA operand must be 16-byte aligned with a 16-byte-multiple row pitch");
+        return HDS_ERR_BAD_ARG;
+    }
+    cuuint64_t gdim[2] = {inner, outer};
+    cuuint64_t gstride[1] = {pitch_bytes};
+    cuuint32_t box[2] = {box_inner, box_outer};
+    cuuint32_t estr[2] = {1, 1};
+    CUresult r = enc(map, CU_TENSOR_MAP_DATA_TYPE_UINT8, 2, const_cast<void*>(base), gdim, gstride, box, estr,
+                     CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                     CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (r != CUDA_SUCCESS) {
+        set_error("cuTensorMapEncodeTiled (8-bit) failed");
+        return HDS_ERR_DRIVER;
+    }
+    return HDS_OK;
+}
+
 // 3D tensor [d2, d1, d0] of 16-bit elements (d0 innermost), strides in bytes for d1 and d2.
 inline int make_tmap_3d_16b(CUtensorMap* map, const void* base, uint64_t d0, uint64_t d1, uint64_t d2,
                             uint64_t stride1_bytes, uint64_t stride2_bytes, uint32_t box0, uint32_t box1,

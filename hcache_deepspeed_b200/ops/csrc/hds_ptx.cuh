@@ -254,6 +254,21 @@ __host__ __device__ constexpr uint32_t make_idesc_f16(uint32_t m, uint32_t n, bo
            ((b_mn_major ? 1u : 0u) << 16) | ((n >> 3) << 17) | ((m >> 4) << 24);
 }
 
+// Instruction descriptor for kind::f8f6f4 with both operands E4M3 (format code 0), D = f32, K-major operands.
+__host__ __device__ constexpr uint32_t make_idesc_f8(uint32_t m, uint32_t n) {
+    return (1u << 4) | ((n >> 3) << 17) | ((m >> 4) << 24);
+}
+// D[tmem] (+)= A[smem] * B[smem], 8-bit float operands, M x N x 32 per instruction
+__device__ __forceinline__ void umma_f8_ss(uint32_t tmem_d, uint64_t desc_a, uint64_t desc_b, uint32_t idesc,
+                                           uint32_t accumulate) {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "setp.ne.b32 p, %4, 0;\n\t"
+        "tcgen05.mma.cta_group::1.kind::f8f6f4 [%0], %1, %2, %3, p;\n\t}\n"
+        ::"r"(tmem_d), "l"(desc_a), "l"(desc_b), "r"(idesc), "r"(accumulate)
+        : "memory");
+}
+
 // --------------------------------------------------------------------------------------------
 // global memory helpers
 // --------------------------------------------------------------------------------------------

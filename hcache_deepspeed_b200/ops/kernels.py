@@ -12,7 +12,7 @@ Reference counterparts: the ``DSKernelBase`` callables under
 from __future__ import annotations
 
 import ctypes
-from typing import Optional, Sequence
+from typing import Optional, Sequence, Tuple
 
 import torch
 
@@ -392,6 +392,42 @@ def moe_gemm(a: torch.Tensor, w_stacked: torch.Tensor, pad_off: torch.Tensor, n_
                                         N, K, _dt(a), EPI_GATED if gated else EPI_STORE, act, _p(out), out.stride(0),
                                         _stream())
     native.check(rc, "hds_moe_gemm")
+    _count()
+    return out
+
+
+def quantize_fp8_rows(x: torch.Tensor, q: Optional[torch.Tensor] = None,
+                      scales: Optional[torch.Tensor] = None) -> Tuple[torch.Tensor, torch.Tensor]:
+    """Row-wise E4M3 quantisation: ``q[r] = e4m3(x[r] / scales[r])`` with ``scales[r] = amax(x[r]) / 448``.
+    Rows are tokens for activations and output channels for weights. ``q`` is ``uint8`` storage of the fp8 codes."""
+    _check_2d(x, "x")
+    rows, K = x.shape
+    if q is None:
+        q = torch.empty(rows, K, dtype=torch.uint8, device=x.device)
+    if scales is None:
+        scales = torch.empty(rows, dtype=torch.float32, device=x.device)
+    rc = native.cuda_lib().hds_quantize_fp8_rows(_p(x), x.stride(0), rows, K, _dt(x), _p(q), q.stride(0), _p(scales),
+                                                 _stream())
+    native.check(rc, "hds_quantize_fp8_rows")
+    _count()
+    return q, scales
+
+
+def gemm_fp8(aq: torch.Tensor, a_scale: torch.Tensor, wq: torch.Tensor, w_scale: torch.Tensor, out: torch.Tensor,
+             bias: Optional[torch.Tensor] = None, act: int = ACT_IDENTITY, gated: bool = False, bn: int = 0) -> torch.Tensor:
+    """``out = epilogue((aq @ wq.T) * a_scale[:, None] * w_scale[None, :] + bias)`` with E4M3 operands on
+    ``tcgen05.mma.kind::f8f6f4`` (fp32 accumulation in TMEM). ``aq``: [M, K] uint8, ``wq``: [N, K] uint8."""
+    _check_2d(aq, "aq")
+    _check_2d(wq, "wq")
+    _check_2d(out, "out")
+    M, K = aq.shape
+    N = wq.shape[0]
+    assert wq.shape[1] == K and aq.dtype == torch.uint8 and wq.dtype == torch.uint8
+    assert a_scale.dtype == torch.float32 and w_scale.dtype == torch.float32
+    rc = native.cuda_lib().hds_gemm_fp8(_p(aq), aq.stride(0), _p(a_scale), _p(wq), wq.stride(0), _p(w_scale), M, N, K,
+                                        _dt(out), EPI_GATED if gated else EPI_STORE, act, _p(bias), _p(out), out.stride(0),
+                                        bn, _stream())
+    native.check(rc, "hds_gemm_fp8")
     _count()
     return out
 

@@ -212,6 +212,19 @@ int hds_moe_gemm(const void* A, int64_t lda, const void* W_stacked, int64_t ldw,
 int hds_moe_gather(const void* y, int64_t ldy, const int32_t* mapped_slots, const float* scores, float* out, int64_t ldo,
                    int T, int k, int H, int dtype, void* stream);
 
+/* ---- FP8 (E4M3) W8A8 GEMM on tcgen05 kind::f8f6f4 ----------------------------------------------------------------
+ * hds_quantize_fp8_rows: q[r, :] = e4m3(x[r, :] / scales[r]), scales[r] = amax(x[r, :]) / 448 (per token for
+ * activations, per output channel for weights). ldx in elements, ldq in bytes.
+ * hds_gemm_fp8: out[M,N] = epilogue((Aq Wq^T) * a_scale[m] * w_scale[n] + bias); epilogue / act / bias as hds_gemm.
+ * lda / ldw are row pitches in bytes (multiples of 16). bn: 0 = auto, else 64 / 128 / 256.
+ * Ref role: inference/v2/kernels/core_ops/cuda_linear (weight-only FP6, sm_80 only) + quantization_mode of
+ * inference/v2/config_v2.py:19-26. */
+int hds_quantize_fp8_rows(const void* x, int64_t ldx, int rows, int K, int dtype, void* q, int64_t ldq, float* scales,
+                          void* stream);
+int hds_gemm_fp8(const void* Aq, int64_t lda, const float* a_scale, const void* Wq, int64_t ldw, const float* w_scale,
+                 int M, int N, int K, int out_dtype, int epilogue, int act, const void* bias, void* out, int64_t ldo,
+                 int bn, void* stream);
+
 /* ---- group-wise quantizers (ref: csrc/quantization, csrc/fp_quantizer) ------------------------------------ */
 /* dtype codes: 0 bf16, 1 fp16, 2 fp32. Integer: bits 4 or 8; params[g] = (scale, offset): value = code * scale + offset.
  * 4-bit codes are packed two per byte (low nibble first). */

@@ -76,3 +76,50 @@ def test_fused_lion_matches_reference():
         opt.step()
         lion_reference(w, g, m, 1e-3, 0.9, 0.999, 0.1)
     torch.testing.assert_close(p.detach().cpu(), w, rtol=1e-5, atol=1e-6)
+
+
+@pytest.mark.parametrize("dtype", [torch.bfloat16, torch.float16])
+def test_quantize_fp8_rows(dtype):
+    from hcache_deepspeed_b200.ops import kernels as K
+    torch.manual_seed(0)
+    x = (torch.randn(37, 1000, device="cuda") * torch.logspace(-2, 2, 37, device="cuda")[:, None]).to(dtype)
+    x[5] = 0
+    q, s = K.quantize_fp8_rows(x)
+    amax = x.float().abs().amax(dim=1)
+    want_s = torch.where(amax > 0, amax / 448.0, torch.ones_like(amax))
+    torch.testing.assert_close(s, want_s, rtol=1e-6, atol=0)
+    want_q = (x.float() / want_s[:, None]).to(torch.float8_e4m3fn)
+    got = q.view(torch.float8_e4m3fn).float()
+    # identical rounding except where the fp32 division lands within an ulp of a tie
+    assert (got != want_q.float()).float().mean() < 1e-3
+    deq = got * s[:, None]
+    assert ((deq - x.float()).abs() <= 0.0625 * amax[:, None] + 1e-12).all()
+
+
+@pytest.mark.parametrize("dtype", [torch.bfloat16, torch.float16])
+@pytest.mark.parametrize("M,N,Kd", [(1, 256, 128), (100, 1000, 2096), (300, 4096, 4096), (2048, 1376, 512)])
+@pytest.mark.parametrize("mode", ["store", "gated"])
+@pytest.mark.parametrize("bn", [0, 64, 128, 256])
+def test_gemm_fp8(dtype, M, N, Kd, mode, bn):
+    """E4M3 x E4M3 -> fp32 (TMEM) GEMM against an fp32 matmul of the de-quantised operands."""
+    from hcache_deepspeed_b200.ops import kernels as K
+    torch.manual_seed(M + N)
+    a = torch.randn(M, Kd, device="cuda").to(dtype)
+    w = (torch.randn(N, Kd, device="cuda") * Kd ** -0.5).to(dtype)
+    bias = torch.randn(N, device="cuda").to(dtype)
+    aq, a_s = K.quantize_fp8_rows(a)
+    wq, w_s = K.quantize_fp8_rows(w)
+    gated = mode == "gated"
+    out = torch.empty(M, N // 2 if gated else N, dtype=dtype, device="cuda")
+    K.gemm_fp8(aq, a_s, wq, w_s, out, bias=bias, act=K.ACT_SILU if gated else K.ACT_IDENTITY, gated=gated, bn=bn)
+    ad = aq.view(torch.float8_e4m3fn).float() * a_s[:, None]
+    wd = wq.view(torch.float8_e4m3fn).float() * w_s[:, None]
+    want = ad @ wd.t() + bias.float()
+    if gated:
+        want = torch.nn.functional.silu(want[:, 0::2]) * want[:, 1::2]
+    tol = dict(rtol=2e-2, atol=2e-2) if dtype == torch.bfloat16 else dict(rtol=4e-3, atol=4e-3)
+    torch.testing.assert_close(out.float(), want, **tol)
+    # and the quantised product tracks the unquantised one (fp8 error, not a wiring error)
+    full = a.float() @ w.float().t() + bias.float()
+    if not gated:
+        assert (out.float() - full).abs().mean() < 0.05 * full.abs().mean() + 0.02

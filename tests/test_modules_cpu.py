@@ -47,3 +47,22 @@ def test_registry_and_implementations():
     with pytest.raises(ValueError):
         DSLinearRegistry.instantiate_config(ConfigBundle("blas_fp_linear", DSLinearConfig(in_channels=8, out_channels=8,
                                                                                           activation="tanh")))
+
+
+def test_fp8_linear_module_cpu_path():
+    """wf8af8 picks the fp8 linear; its CPU restatement (same quantisation rule as the CUDA path) tracks the fp linear."""
+    from types import SimpleNamespace
+    from hcache_deepspeed_b200.inference.v2.modules import DSLinearConfig, instantiate_linear
+    torch.manual_seed(0)
+    cfg = DSLinearConfig(max_tokens=64, in_channels=128, out_channels=96, activation="identity",
+                         input_dtype=torch.bfloat16, output_dtype=torch.bfloat16)
+    eng = SimpleNamespace(quantization=SimpleNamespace(quantization_mode="wf8af8"))
+    lin = instantiate_linear(cfg, eng)
+    assert lin.name() == "fp8_tcgen05_linear"
+    w = (torch.randn(96, 128) * 128 ** -0.5).to(torch.bfloat16)
+    x = torch.randn(10, 128).to(torch.bfloat16)
+    wq = lin.transform_param(w)
+    assert wq.dtype == torch.uint8 and wq.scales.shape == (96, )
+    y = lin(x, wq)
+    want = x.float() @ w.float().t()
+    assert (y.float() - want).abs().mean() < 0.05 * want.abs().mean() + 0.02

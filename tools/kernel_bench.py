@@ -205,10 +205,25 @@ def bench_norm():
         report(f"pre_rmsnorm_f32delta rows{rows} cols4096", med, mn, bytes_=rows * 4096 * (2 + 4 + 4 + 2 + 2))
 
 
+def bench_gemm_fp8():
+    for (M, N, Kd) in [(4096, 4096, 4096), (4096, 12288, 4096), (4096, 4096, 11008), (8192, 8192, 8192), (32768, 12288, 4096)]:
+        a, w = rand(M, Kd), rand(N, Kd, scale=Kd ** -0.5)
+        aq, a_s = K.quantize_fp8_rows(a)
+        wq, w_s = K.quantize_fp8_rows(w)
+        out = torch.empty(M, N, device=dev, dtype=torch.bfloat16)
+        for bn in (128, 256):
+            med, mn = timeit(lambda: K.gemm_fp8(aq, a_s, wq, w_s, out, bn=bn))
+            report(f"gemm_fp8 M{M} N{N} K{Kd} bn{bn}", med, mn, flops=2.0 * M * N * Kd)
+        med, mn = timeit(lambda: K.quantize_fp8_rows(a, aq, a_s))
+        report(f"quantize_fp8_rows M{M} K{Kd}", med, mn, bytes_=M * Kd * 3)
+        med, mn = timeit(lambda: K.gemm(a, w, out=out, bn=256))
+        report(f"gemm_bf16 M{M} N{N} K{Kd} bn256", med, mn, flops=2.0 * M * N * Kd)
+
+
 if __name__ == "__main__":
     which = sys.argv[1:] or ["gemm", "decode_gemm", "restore", "attn_decode", "attn_prefill", "norm"]
     table = {"gemm": bench_gemm, "decode_gemm": bench_decode_gemm, "restore": bench_restore,
-             "attn_decode": bench_attention_decode, "tiled": bench_tiled, "attn_prefill": bench_attention_prefill, "norm": bench_norm}
+             "attn_decode": bench_attention_decode, "tiled": bench_tiled, "attn_prefill": bench_attention_prefill, "norm": bench_norm, "gemm_fp8": bench_gemm_fp8}
     for w in which:
         table[w]()
     os.makedirs("gpurun_out", exist_ok=True)
