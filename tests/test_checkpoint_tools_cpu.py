@@ -36,3 +36,39 @@ def test_universal_checkpoint_resumes_with_other_dp_degree(tmp_path):
     assert res[0]["restored"] == len(states[0]) and res[0]["exp_avg_norm"] > 0
     for k, v in states[0].items():
         torch.testing.assert_close(res[0]["state"][k], v, rtol=1e-6, atol=1e-7)
+
+
+def test_reshape_3d_maps_and_zero_checkpoint(tmp_path):
+    """(pp, tp, dp) contraction maps and ZeRO optimizer-file merging (reference: checkpoint/reshape_*.py, zero_checkpoint.py)."""
+    import torch
+    from hcache_deepspeed_b200.checkpoint import reshape as R
+    m = R.reshape_meg_2d_parallel(4, 4, 2, 2)
+    assert m.get_data(0, 0) == [0, 1, 4, 5] and m.get_data(1, 1) == [10, 11, 14, 15]
+    maps = R.model_3d_desc(2, 2, 2).reshape(R.model_3d_desc(1, 1, 1))
+    assert len(maps) == 1 and maps[0].get_data(0, 0) == [0, 4, 1, 5, 2, 6, 3, 7]
+    maps = R.model_3d_desc(1, 2, 4).reshape(R.model_3d_desc(1, 2, 2))
+    assert maps[0].get_data(0, 1) == [1, 3] and maps[1].get_data(0, 1) == [5, 7]
+    ok, errs = R.model_3d_desc(1, 2, 2).can_reshape(R.model_3d_desc(1, 4, 2))
+    assert not ok and "TP" in errs[0]
+    tp, pp, dp = R.get_mpu_ranks(2, 4, 2)
+    assert tp[0] == [0, 1] and pp[0] == [0, 4, 8, 12] and dp[:2] == [[0, 2], [1, 3]]
+
+    # a tp=1, pp=1, dp=4 ZeRO checkpoint: flat fp32 partitions of 6 elements, the last rank carries 2 of padding
+    for r in range(4):
+        sd = {"optimizer_state_dict": {
+            "base_optimizer_state": {"state": {0: {"exp_avg": torch.full((6, ), float(r)), "step": 3}}},
+            "group_paddings": [2 if r == 3 else 0], "partition_count": [4],
+            "single_partition_of_fp32_groups": [torch.arange(6.0) + 10 * r]}}
+        torch.save(sd, R.get_zero_ckpt_name_for_rank(str(tmp_path), r, 0))
+    torch.save({}, R.get_model_ckpt_name_for_rank(str(tmp_path), "00"))
+    ck = R.ZeROCheckpoint(str(tmp_path))
+    assert (ck.get_src_pp_degree(), ck.get_src_tp_degree(), ck.get_src_dp_degree()) == (1, 1, 4)
+    ck.reshape(R.model_3d_desc(1, 1, 2))
+    assert ck.get_file_indices_for_rank(0, 0, 1) == [2, 3]
+    sd = ck.get_state_for_rank(0, 0, 1)["optimizer_state_dict"]
+    assert sd["partition_count"] == [2] and sd["group_paddings"] == [0]
+    ea = sd["base_optimizer_state"]["state"][0]["exp_avg"]
+    assert ea.tolist() == [2.0] * 6 + [3.0] * 4            # rank 3's padding stripped before the merge
+    assert sd["single_partition_of_fp32_groups"][0].numel() == 12
+    c = R.clone_tensors_for_torch_save({"a": [torch.ones(4)[:2]]})
+    assert c["a"][0].untyped_storage().size() == 8
