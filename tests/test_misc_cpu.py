@@ -213,3 +213,26 @@ def test_multinode_runner_commands():
     assert cmds["mvapich"][-3:] == ["train.py", "--x", "1"]
     with pytest.raises(ValueError):
         RUNNERS["mpich"](args, "x").get_cmd({}, {"a": [0], "b": [0, 1]})
+
+
+def test_nvme_tune_sweep(tmp_path):
+    """Sweep -> JSON-lines logs -> best "aio" block (reference: nvme/perf_run_sweep.py, perf_generate_param.py)."""
+    from hcache_deepspeed_b200.nvme import tune
+    assert tune.parse_size("8M") == 8 << 20 and tune.parse_size("400M") == 400 << 20 and tune.parse_size(4096) == 4096
+    space = {"block_size": ["256K", "1M"], "queue_depth": [8], "io_parallel": [1, 2], "use_direct": [False]}
+    assert len(tune.sweep_points(space)) == 4
+    out = tune.sweep_main(["--nvme_dir", str(tmp_path / "d0"), "--io_size", "2M", "--log_dir", str(tmp_path / "logs")]
+                          + ["--sweep_config", _write_json(tmp_path / "space.json", space)])
+    aio = out["aio"]
+    assert aio["block_size"] in (256 << 10, 1 << 20) and aio["intra_op_parallelism"] in (1, 2) and aio["queue_depth"] == 8
+    assert out["read_GBps"] > 0 and out["write_GBps"] > 0
+    assert len(os.listdir(tmp_path / "logs" / "read")) == 4 and len(os.listdir(tmp_path / "logs" / "write")) == 4
+    assert not os.path.exists(tmp_path / "d0" / "hds_nvme_tune.bin")
+    assert tune.generate_main(str(tmp_path / "logs"))["aio"] == aio
+
+
+def _write_json(path, obj):
+    import json
+    with open(path, "w") as f:
+        json.dump(obj, f)
+    return str(path)
