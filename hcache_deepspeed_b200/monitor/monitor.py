@@ -103,11 +103,60 @@ class WandbMonitor(Monitor):
             self._wandb.log({name: value}, step=step)
 
 
+class EventsLogScheduler:
+    """Rate limiter: an event name is logged at most once per ``samples_log_interval`` samples (comet.py:70-92)."""
+
+    def __init__(self, samples_log_interval: int):
+        self._interval = samples_log_interval
+        self._last = {}
+
+    def needs_logging(self, name: str, current_sample: int) -> bool:
+        last = self._last.get(name)
+        if last is None or current_sample - last >= self._interval:
+            self._last[name] = current_sample
+            return True
+        return False
+
+
+class CometMonitor(Monitor):
+    """Comet experiment sink (``deepspeed/monitor/comet.py:23-68``); disabled with a warning when ``comet_ml`` is absent."""
+
+    def __init__(self, config, experiment=None):
+        super().__init__(config)
+        self._experiment = experiment
+        self._scheduler = EventsLogScheduler(config.samples_log_interval)
+        if self.enabled and _rank() == 0 and experiment is None:
+            try:
+                import comet_ml
+                self._experiment = comet_ml.start(api_key=config.api_key, project=config.project, workspace=config.workspace,
+                                                  experiment_key=config.experiment_key, mode=config.mode, online=config.online)
+                if config.experiment_name is not None:
+                    self._experiment.set_name(config.experiment_name)
+            except Exception as e:
+                logger.warning(f"Comet monitor disabled: {e}")
+                self.enabled = False
+
+    @property
+    def experiment(self):
+        return self._experiment
+
+    @property
+    def samples_log_interval(self) -> int:
+        return self._scheduler._interval
+
+    def write_events(self, event_list: Iterable[Event]) -> None:
+        if not self.enabled or self._experiment is None or _rank() != 0:
+            return
+        for name, value, step in event_list:
+            if self._scheduler.needs_logging(name, step):
+                self._experiment.log_metric(name=name, value=value, step=step)
+
+
 class MonitorMaster(Monitor):
 
     def __init__(self, monitor_config: DeepSpeedMonitorConfig):
         self.enabled = monitor_config.enabled
-        self.tb_monitor = self.wandb_monitor = self.csv_monitor = None
+        self.tb_monitor = self.wandb_monitor = self.csv_monitor = self.comet_monitor = None
         if _rank() == 0:
             if monitor_config.tensorboard.enabled:
                 self.tb_monitor = TensorBoardMonitor(monitor_config.tensorboard)
@@ -115,11 +164,13 @@ class MonitorMaster(Monitor):
                 self.wandb_monitor = WandbMonitor(monitor_config.wandb)
             if monitor_config.csv_monitor.enabled:
                 self.csv_monitor = CSVMonitor(monitor_config.csv_monitor)
+            if monitor_config.comet.enabled:
+                self.comet_monitor = CometMonitor(monitor_config.comet)
 
     def write_events(self, event_list: Iterable[Event]) -> None:
         if _rank() != 0:
             return
         event_list = list(event_list)
-        for m in (self.tb_monitor, self.wandb_monitor, self.csv_monitor):
+        for m in (self.tb_monitor, self.wandb_monitor, self.csv_monitor, self.comet_monitor):
             if m is not None:
                 m.write_events(event_list)

@@ -236,3 +236,22 @@ def _write_json(path, obj):
     with open(path, "w") as f:
         json.dump(obj, f)
     return str(path)
+
+
+def test_comet_monitor_rate_limit():
+    from hcache_deepspeed_b200.monitor import CometMonitor, EventsLogScheduler
+    from hcache_deepspeed_b200.monitor.config import CometConfig
+    s = EventsLogScheduler(100)
+    assert [s.needs_logging("loss", x) for x in (0, 50, 100, 150, 230)] == [True, False, True, False, True]
+
+    class _Exp:
+        def __init__(self):
+            self.logged = []
+
+        def log_metric(self, name, value, step):
+            self.logged.append((name, value, step))
+
+    exp = _Exp()
+    m = CometMonitor(CometConfig(enabled=True, samples_log_interval=10), experiment=exp)
+    m.write_events([("lr", 0.1, 0), ("lr", 0.2, 5), ("loss", 3.0, 5), ("lr", 0.3, 10)])
+    assert exp.logged == [("lr", 0.1, 0), ("loss", 3.0, 5), ("lr", 0.3, 10)]
