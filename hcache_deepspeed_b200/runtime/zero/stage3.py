@@ -48,12 +48,20 @@ class DeepSpeedZeRoOffload:
 
     @staticmethod
     def _own_params(m: torch.nn.Module) -> List[torch.nn.Parameter]:
-        ps = [p for p in m.parameters(recurse=False) if is_zero_param(p)]
+        # a module flagged by utils.z3_leaf_module owns its whole subtree (children carry no hooks of their own)
+        ps = [p for p in m.parameters(recurse=bool(getattr(m, "_z3_leaf", False))) if is_zero_param(p)]
         ps += [p for p in getattr(m, "_external_params", {}).values() if is_zero_param(p)]
         return ps
 
     def _install(self, root: torch.nn.Module):
+        under_leaf = set()
         for m in root.modules():
+            if id(m) in under_leaf:
+                continue
+            if getattr(m, "_z3_leaf", False):
+                under_leaf.update(id(c) for c in m.modules() if c is not m)
+                for p in m.parameters():
+                    p.ds_z3_leaf_module = m
             if not self._own_params(m):
                 continue
             self.hooks.append(m.register_forward_pre_hook(self._pre_forward))

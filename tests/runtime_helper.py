@@ -4,16 +4,21 @@ import os
 import torch
 
 
+class Stack(torch.nn.ModuleList):
+    def forward(self, x):
+        for l in self:
+            x = torch.tanh(l(x))
+        return x
+
+
 class TinyNet(torch.nn.Module):
     def __init__(self, hidden=32, nlayers=3):
         super().__init__()
-        self.layers = torch.nn.ModuleList([torch.nn.Linear(hidden, hidden) for _ in range(nlayers)])
+        self.layers = Stack([torch.nn.Linear(hidden, hidden) for _ in range(nlayers)])
         self.head = torch.nn.Linear(hidden, 1)
 
     def forward(self, x, y):
-        for l in self.layers:
-            x = torch.tanh(l(x))
-        return torch.nn.functional.mse_loss(self.head(x).squeeze(-1), y)
+        return torch.nn.functional.mse_loss(self.head(self.layers(x)).squeeze(-1), y)
 
 
 def make_batches(n, bs, hidden=32, seed=0):
@@ -53,7 +58,14 @@ def zero_worker(rank, world, stage, steps, gas, offload, dtype_name, ckpt_dir):
         cfg["bf16"] = {"enabled": True}
     elif dtype_name == "fp16":
         cfg["fp16"] = {"enabled": True, "initial_scale_power": 8}
+    if os.environ.get("HDS_TEST_Z3_LEAF") == "1":
+        from hcache_deepspeed_b200.utils.z3_leaf_module import get_z3_leaf_modules, set_z3_leaf_modules, z3_leaf_parameter
+        assert set_z3_leaf_modules(model, ["Stack"]) == [model.layers]
     engine, opt, _, _ = ds.initialize(model=model, config=cfg)
+    if os.environ.get("HDS_TEST_Z3_LEAF") == "1":
+        assert get_z3_leaf_modules(engine.module) == [engine.module.layers]
+        assert all(z3_leaf_parameter(p) for p in engine.module.layers.parameters())
+        assert not any(z3_leaf_parameter(p) for p in engine.module.head.parameters())
     global_bs = micro * gas * world
     losses = []
     for step, (x, y) in enumerate(make_batches(steps, global_bs, hidden)):

@@ -255,3 +255,30 @@ def test_comet_monitor_rate_limit():
     m = CometMonitor(CometConfig(enabled=True, samples_log_interval=10), experiment=exp)
     m.write_events([("lr", 0.1, 0), ("lr", 0.2, 5), ("loss", 3.0, 5), ("lr", 0.3, 10)])
     assert exp.logged == [("lr", 0.1, 0), ("loss", 3.0, 5), ("lr", 0.3, 10)]
+
+
+def test_small_utils():
+    from hcache_deepspeed_b200.utils import bwc, mixed_precision_linkage as mpl
+    from hcache_deepspeed_b200.utils.torch import required_torch_version
+    from hcache_deepspeed_b200.utils.types import GATED_ACTIVATION_TYPES, ActivationFuncType, NormType
+    assert bwc.bwc_tensor_model_parallel_rank(None) == 0 and bwc.bwc_pipeline_parallel_world_size(None) == 1
+    old = types.SimpleNamespace(get_model_parallel_rank=lambda: 3, get_model_parallel_world_size=lambda: 4,
+                                get_model_parallel_group=lambda: "g", get_pipe_parallel_world_size=lambda: 2)
+    assert bwc.bwc_tensor_model_parallel_rank(old) == 3 and bwc.bwc_tensor_model_parallel_world_size(old) == 4
+    assert bwc.bwc_tensor_model_parallel_group(old) == "g" and bwc.bwc_pipeline_parallel_world_size(old) == 2
+    assert required_torch_version(min_version="2.0") and not required_torch_version(max_version="1.13")
+    assert ActivationFuncType.GATED_SILU in GATED_ACTIVATION_TYPES and NormType.RMSNorm == 3
+    # lp params of 6, 10, 8 elements; this rank owns flat elements [4, 16): all of none, tail of p0, all of... etc.
+    ps = [torch.arange(6.0).bfloat16(), torch.arange(10.0).bfloat16(), torch.arange(8.0).bfloat16()]
+    flat = torch.zeros(12)
+    mpl.link_hp_params(ps, flat, partition_start=4, partition_size=12)
+    m0, m1, m2 = (p._hp_mapping for p in ps)
+    assert (m0.lp_fragment_address.start, m0.lp_fragment_address.numel, m0.hp_fragment_address.start) == (4, 2, 0)
+    assert (m1.lp_fragment_address.start, m1.lp_fragment_address.numel, m1.hp_fragment_address.start) == (0, 10, 2)
+    assert m2 is None or m2.lp_fragment_address.numel == 0 or True
+    assert ps[2]._hp_mapping is None  # [16, 24) lies outside the partition
+    for m in (m0, m1):
+        m.update_hp()
+    assert flat.tolist() == [4, 5] + list(range(10))
+    mpl.lazy_init_hp_params_optimizer_state(ps[:2], flat, {flat: {"exp_avg": torch.arange(12.0), "step": torch.tensor(1)}})
+    assert m1.get_hp_fragment("exp_avg").tolist() == list(range(2, 12))

@@ -213,6 +213,17 @@ def test_zero_stages_match_reference_2ranks(stage, gas, offload, tmp_path):
     assert mean == pytest.approx(want, rel=5e-4, abs=5e-5)
 
 
+def test_zero3_leaf_module_2ranks(monkeypatch):
+    """A module flagged with set_z3_leaf_modules gathers its whole subtree from one hook; results are unchanged."""
+    monkeypatch.setenv("HDS_TEST_Z3_LEAF", "1")
+    steps, world = 4, 2
+    want, want_state = reference_run(steps=steps, global_bs=4 * world)
+    res = run_distributed(zero_worker, world, 3, steps, 1, False, "fp32", None)
+    for r in res:
+        for k, v in want_state.items():
+            torch.testing.assert_close(r["state"][k], v, rtol=2e-4, atol=2e-5)
+
+
 @pytest.mark.parametrize("stage,dtype", [(0, "bf16"), (2, "bf16"), (2, "fp16"), (0, "fp16")])
 def test_mixed_precision_trains(stage, dtype):
     res = run_distributed(zero_worker, 2, stage, 12, 1, False, dtype, None)
