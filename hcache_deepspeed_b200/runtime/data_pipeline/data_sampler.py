@@ -32,7 +32,19 @@ class DeepSpeedDataSampler:
         if self.curriculum_enabled:
             for metric, mcfg in (cl.get("curriculum_metrics") or {}).items():
                 self.curriculum_schedulers[metric] = CurriculumScheduler(mcfg)
+                if metric not in self.difficulties and mcfg.get("index_to_sample_path") and mcfg.get("index_to_metric_path"):
+                    self.difficulties[metric] = self._load_difficulties(mcfg["index_to_sample_path"],
+                                                                        mcfg["index_to_metric_path"])
         self.batch: List[int] = []
+
+    def _load_difficulties(self, index_to_sample_path: str, index_to_metric_path: str) -> np.ndarray:
+        """Per-sample difficulty from the data analyzer's ``*_index_to_sample`` / ``*_index_to_metric`` files."""
+        from .data_sampling.indexed_dataset import MMapIndexedDataset
+        i2s, i2m = MMapIndexedDataset(index_to_sample_path), MMapIndexedDataset(index_to_metric_path)
+        out = np.zeros(self.total_samples, dtype=np.int64)
+        for j in range(len(i2s)):
+            out[np.asarray(i2s[j], dtype=np.int64)] = int(i2m[j][0])
+        return out
 
     def __len__(self):
         return self.total_samples

@@ -1,0 +1,168 @@
+"""Indexed datasets, the offline data analyzer and token-budget batching (reference tests:
+tests/unit/runtime/test_data_efficiency.py, data_sampling/data_analyzer.py::test_compare_both_data_analyzers)."""
+import numpy as np
+import pytest
+import torch
+
+from hcache_deepspeed_b200.runtime.data_pipeline.data_sampling import (DataAnalyzer, DistributedDataAnalyzer, MMapIndexedDataset,
+                                                                        MMapIndexedDatasetBuilder, batch_by_seqlens,
+                                                                        get_dataloader_and_lr_scheduler_for_variable_batch_size,
+                                                                        load_sample_to_metric, scale_lr)
+from hcache_deepspeed_b200.runtime.data_pipeline.data_sampling import indexed_dataset as ixd
+from hcache_deepspeed_b200.runtime.data_pipeline.data_sampling.utils import find_fit_int_dtype, split_index
+
+
+def test_mmap_indexed_dataset_roundtrip(tmp_path):
+    rng = np.random.default_rng(0)
+    docs = [rng.integers(0, 50000, size=n) for n in (5, 1, 17, 0, 9)]
+    prefix = str(tmp_path / "ds")
+    b = ixd.make_builder(ixd.data_file_path(prefix), "mmap", vocab_size=50000)
+    for d in docs:
+        b.add_item(torch.from_numpy(d))
+        b.end_document()
+    b.finalize(ixd.index_file_path(prefix))
+    assert ixd.infer_dataset_impl(prefix) == "mmap" and ixd.dataset_exists(prefix)
+    ds = ixd.make_dataset(prefix, "infer")
+    assert len(ds) == 5 and ds.dtype == np.uint16 and ds.sizes.tolist() == [5, 1, 17, 0, 9]
+    assert ds.doc_idx.tolist() == [0, 1, 2, 3, 4, 5]
+    for i, d in enumerate(docs):
+        assert ds[i].tolist() == d.tolist()
+    assert ds.get(2, offset=3, length=4).tolist() == docs[2][3:7].tolist()
+    assert [x.tolist() for x in ds[1:3]] == [docs[1].tolist(), docs[2].tolist()]
+    # header layout is the Megatron one
+    raw = open(ixd.index_file_path(prefix), "rb").read()
+    assert raw[:9] == b"MMIDIDX\x00\x00" and raw[9:17] == (1).to_bytes(8, "little") and raw[17] == 6
+    # merge
+    b2 = MMapIndexedDatasetBuilder(ixd.data_file_path(prefix + "2"), dtype=np.uint16)
+    b2.add_item_numpy(np.array([7, 8]))
+    b2.end_document()
+    b2.merge_file_(prefix)
+    b2.finalize(ixd.index_file_path(prefix + "2"))
+    m = MMapIndexedDataset(prefix + "2")
+    assert len(m) == 6 and m[0].tolist() == [7, 8] and m[3].tolist() == docs[2].tolist() and m.doc_idx.tolist() == list(range(7))
+    import pickle
+    assert len(pickle.loads(pickle.dumps(m))) == 6
+
+
+class _Seqs(torch.utils.data.Dataset):
+    def __init__(self, n=203, seed=0):
+        self.lens = np.random.default_rng(seed).integers(1, 40, size=n)
+
+    def __len__(self):
+        return len(self.lens)
+
+    def __getitem__(self, i):
+        return torch.full((int(self.lens[i]), ), i % 7)
+
+
+def _metrics():
+    names = ["seqlen", "vocab"]
+    fns = [lambda batch: torch.tensor([len(s) for s in batch]),
+           lambda batch: torch.bincount(torch.cat(batch), minlength=7)]
+    return names, fns, ["single_value_per_sample", "accumulate_value_over_samples"]
+
+
+@pytest.mark.parametrize("workers", [1, 3])
+def test_data_analyzer_map_reduce(tmp_path, workers):
+    ds = _Seqs()
+    names, fns, types_ = _metrics()
+    for w in range(workers):
+        DataAnalyzer(ds, num_workers=workers, worker_id=w, batch_size=16, metric_names=names, metric_functions=fns,
+                     metric_types=types_, save_path=str(tmp_path), collate_fn=list).run_map()
+    DataAnalyzer(ds, num_workers=workers, worker_id=0, metric_names=names, metric_functions=fns, metric_types=types_,
+                 save_path=str(tmp_path)).run_reduce()
+    assert load_sample_to_metric(str(tmp_path), "seqlen").tolist() == ds.lens.tolist()
+    i2m = MMapIndexedDataset(f"{tmp_path}/seqlen/seqlen_index_to_metric")
+    i2s = MMapIndexedDataset(f"{tmp_path}/seqlen/seqlen_index_to_sample")
+    uniq = sorted(set(ds.lens.tolist()))
+    assert [int(i2m[j][0]) for j in range(len(i2m))] == uniq
+    for j, v in enumerate(uniq):
+        assert sorted(i2s[j].tolist()) == np.nonzero(ds.lens == v)[0].tolist()
+    merged = MMapIndexedDataset(f"{tmp_path}/seqlen/seqlen_index_to_sample_percentile_merged")
+    allidx = np.concatenate([merged[j] for j in range(len(merged))])
+    assert sorted(allidx.tolist()) == list(range(len(ds))) and (np.diff(ds.lens[allidx]) >= 0).all()
+    vocab = MMapIndexedDataset(f"{tmp_path}/vocab/vocab_metric_value")[0]
+    want = np.zeros(7, dtype=np.int64)
+    for i, n in enumerate(ds.lens):
+        want[i % 7] += n
+    assert vocab.tolist() == want.tolist()
+
+
+def test_distributed_data_analyzer_single_process(tmp_path):
+    ds = _Seqs(50)
+    names, fns, types_ = _metrics()
+    DistributedDataAnalyzer(ds, batch_size=8, metric_names=names, metric_functions=fns, metric_types=types_,
+                            save_path=str(tmp_path), collate_fn=list).run_map_reduce()
+    assert load_sample_to_metric(str(tmp_path), "seqlen").tolist() == ds.lens.tolist()
+
+
+def test_small_helpers():
+    assert find_fit_int_dtype(0, 255) == np.uint8 and find_fit_int_dtype(0, 256) == np.uint16
+    assert find_fit_int_dtype(-1, 100) == np.int8 and find_fit_int_dtype(-1, 40000) == np.int32
+    assert split_index(0, 10, 3) == [(0, 3), (3, 6), (6, 10)]
+    assert scale_lr(8, 16, 0.1) == pytest.approx(0.2) and scale_lr(8, 32, 0.1, "sqrt") == pytest.approx(0.2)
+    assert scale_lr(8, 32, 0.1, None) == 0.1
+
+
+@pytest.mark.parametrize("order", ["dataloader", "seqlen", "random"])
+@pytest.mark.parametrize("same_size", [False, True])
+def test_batch_by_seqlens(order, same_size):
+    ds = _Seqs(300, seed=3)
+    ebs = 4
+    mb_ids, batch_sizes, max_lens = batch_by_seqlens(ds.lens, max_tokens=100, min_batch_size=1, max_batch_size=8,
+                                                     sequence_picking_order=order, effective_batch_size=ebs,
+                                                     required_microbatches_of_same_size=same_size, seed=1)
+    assert len(mb_ids) == ebs * len(batch_sizes) == ebs * len(max_lens)
+    seen = []
+    for k, (batch_id, ids) in enumerate(mb_ids):
+        assert batch_id == k // ebs and 1 <= len(ids) <= 8 and ds.lens[ids].sum() <= 100
+        seen += ids
+    assert len(seen) == len(set(seen))                      # nothing is used twice
+    assert len(seen) >= 0.9 * len(ds)                       # and the packing is not wasteful
+    for b in range(len(batch_sizes)):
+        mbs = [ids for bid, ids in mb_ids if bid == b]
+        assert sum(len(m) for m in mbs) == batch_sizes[b] and max(ds.lens[i] for m in mbs for i in m) == max_lens[b]
+        if same_size:
+            assert len({len(m) for m in mbs}) == 1
+
+
+def test_variable_batch_dataloader_and_lr():
+    ds = _Seqs(120, seed=5)
+    model = torch.nn.Linear(2, 2)
+    opt = torch.optim.SGD(model.parameters(), lr=0.1)
+    sched = torch.optim.lr_scheduler.StepLR(opt, step_size=1, gamma=0.5)
+    seen = []
+    for rank in range(2):
+        loader, lr_sched, io = get_dataloader_and_lr_scheduler_for_variable_batch_size(
+            ds, ds.lens, max_tokens=64, base_batch_size=8, lr_scheduler_or_optimizer=sched if rank == 0 else None,
+            effective_batch_size=2, dataloader_rank=rank, dataloader_num_replicas=2, dataloader_collate_fn=lambda b: b)
+        for batch in loader:
+            assert sum(len(s) for s in batch) <= 64
+            seen.append(len(batch))
+        if rank == 0:
+            sizes = lr_sched.batch_sizes
+            assert opt.param_groups[0]["lr"] == pytest.approx(0.1 * sizes[0] / 8)
+            for step in range(1, 4):
+                opt.step()
+                lr_sched.step()
+                assert opt.param_groups[0]["lr"] == pytest.approx(0.1 * 0.5 ** step * sizes[step % len(sizes)] / 8)
+            sd = lr_sched.state_dict()
+            lr_sched.load_state_dict(sd)
+            assert lr_sched.last_epoch == 3
+    assert sum(seen) >= 0.9 * 120 - 8
+
+
+def test_sampler_reads_analyzer_indexes(tmp_path):
+    from hcache_deepspeed_b200.runtime.data_pipeline.data_sampler import DeepSpeedDataSampler
+    ds = _Seqs(200, seed=9)
+    DataAnalyzer(ds, batch_size=32, metric_names=["seqlen"], metric_functions=[_metrics()[1][0]],
+                 metric_types=["single_value_per_sample"], save_path=str(tmp_path), collate_fn=list).run_map_reduce()
+    cfg = {"data_sampling": {"curriculum_learning": {"enabled": True, "curriculum_metrics": {"seqlen": {
+        "index_to_sample_path": f"{tmp_path}/seqlen/seqlen_index_to_sample",
+        "index_to_metric_path": f"{tmp_path}/seqlen/seqlen_index_to_metric",
+        "min_difficulty": 10, "max_difficulty": 40, "schedule_type": "fixed_linear",
+        "schedule_config": {"total_curriculum_step": 10, "difficulty_step": 1}}}}}}
+    s = DeepSpeedDataSampler(cfg, len(ds), micro_batch_size=4, data_parallel_rank=0, data_parallel_size=2)
+    assert s.difficulties["seqlen"].tolist() == ds.lens.tolist()
+    first = s.get_next_global_batch()
+    assert ds.lens[first].max() <= 13          # early batches only draw easy (short) samples
