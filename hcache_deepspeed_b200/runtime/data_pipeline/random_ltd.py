@@ -104,3 +104,27 @@ class RandomLayerTokenDrop(torch.nn.Module):
         out0 = out[0] if isinstance(out, tuple) else out
         full = scatter_tokens(hidden_states, out0, idx, self.batch_first)
         return (full, ) + tuple(rest) if rest is not None else full
+
+
+def convert_to_random_ltd(model, convert_type, scheduler: RandomLTDScheduler = None, batch_first: bool = True):
+    """Wrap every sub-module of type ``convert_type`` in :class:`RandomLayerTokenDrop`
+    (``data_routing/helper.py:11-25``). ``model`` may be an engine (``.module`` is then converted)."""
+    root = model.module if hasattr(model, "module") and isinstance(model.module, torch.nn.Module) else model
+    targets = [(n, m) for n, m in root.named_modules() if isinstance(m, convert_type) and n]
+    for layer_id, (name, mod) in enumerate(targets):
+        parent_name, _, leaf = name.rpartition(".")
+        parent = root.get_submodule(parent_name) if parent_name else root
+        setattr(parent, leaf, RandomLayerTokenDrop(mod, layer_id, scheduler, batch_first))
+    if hasattr(model, "random_ltd_initialize"):
+        model.random_ltd_initialize()
+    return model
+
+
+def remove_random_ltd_state_dict(state_dict):
+    """Checkpoint keys without the wrapper level, so the file loads into the unconverted model."""
+    return type(state_dict)((k.replace(".random_ltd_layer", ""), v) for k, v in state_dict.items())
+
+
+def save_without_random_ltd(model):
+    root = model.module if hasattr(model, "module") and isinstance(model.module, torch.nn.Module) else model
+    return remove_random_ltd_state_dict(root.state_dict())

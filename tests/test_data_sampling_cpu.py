@@ -166,3 +166,16 @@ def test_sampler_reads_analyzer_indexes(tmp_path):
     assert s.difficulties["seqlen"].tolist() == ds.lens.tolist()
     first = s.get_next_global_batch()
     assert ds.lens[first].max() <= 13          # early batches only draw easy (short) samples
+
+
+def test_convert_to_random_ltd_and_clean_state_dict():
+    from hcache_deepspeed_b200.runtime.data_pipeline.data_routing import (RandomLayerTokenDrop, convert_to_random_ltd,
+                                                                        save_without_random_ltd)
+    model = torch.nn.Sequential(torch.nn.Linear(4, 4), torch.nn.Sequential(torch.nn.Linear(4, 4), torch.nn.ReLU()))
+    keys = list(model.state_dict())
+    convert_to_random_ltd(model, torch.nn.Linear)
+    assert isinstance(model[0], RandomLayerTokenDrop) and isinstance(model[1][0], RandomLayerTokenDrop)
+    assert model[0].layer_id == 0 and model[1][0].layer_id == 1
+    assert any("random_ltd_layer" in k for k in model.state_dict())
+    assert list(save_without_random_ltd(model)) == keys
+    assert model(torch.randn(2, 3, 4)).shape == (2, 3, 4)
