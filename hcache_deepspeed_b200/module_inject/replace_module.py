@@ -46,12 +46,23 @@ class GroupQuantizer:
 
 
 def generic_injection(module, dtype=None, enable_cuda_graph: bool = True):
-    """Diffusers pipelines: cast the heavy sub-modules (unet / vae / text_encoder) to ``dtype``; their attention runs on
-    torch SDPA. (The reference swaps in Triton/CUDA attention blocks, ``replace_module.py:88-181``.)"""
+    """Diffusers pipelines: cast the heavy sub-modules (unet / vae / text_encoder) to ``dtype`` and put them behind
+    CUDA graphs (``DSUNet`` / ``DSVAE`` / ``DSClipEncoder``); their attention runs on torch SDPA. (The reference
+    additionally swaps in Triton/CUDA attention blocks, ``replace_module.py:88-181``.)"""
+    from ..model_implementations.diffusers import DSUNet, DSVAE
+    from ..model_implementations.transformers.clip_encoder import DSClipEncoder
+    wrappers = {"unet": DSUNet, "vae": DSVAE, "text_encoder": DSClipEncoder}
     for name in ("unet", "vae", "text_encoder", "transformer"):
         sub = getattr(module, name, None)
-        if isinstance(sub, torch.nn.Module) and dtype is not None:
+        if not isinstance(sub, torch.nn.Module):
+            continue
+        if dtype is not None:
             sub.to(dtype)
+        if name in wrappers and not isinstance(sub, tuple(wrappers.values())):
+            try:
+                setattr(module, name, wrappers[name](sub, enable_cuda_graph=enable_cuda_graph))
+            except Exception:  # pipelines that validate component types keep the bare module
+                pass
     return module
 
 

@@ -1,0 +1,2 @@
+"""``deepspeed.ops.gds``: GPUDirect Storage operator (cuFile binding, present only where libcufile is)."""
+from ...io.gds import GDSHandle, gds_available  # noqa: F401

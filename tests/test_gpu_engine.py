@@ -127,3 +127,34 @@ def test_async_capture_and_flush():
 def test_smoke_entry():
     import __graft_entry__ as ge
     ge.smoke()
+
+
+def test_graphed_callable_replays_and_tracks_inputs():
+    """GraphedCallable (DSUNet / DSVAE / DSClipEncoder back end): capture once per signature, replay with fresh inputs."""
+    from hcache_deepspeed_b200.model_implementations.diffusers import DSUNet
+    from hcache_deepspeed_b200.model_implementations.features import GraphedCallable
+    lin = torch.nn.Linear(64, 64).cuda().half()
+    g = GraphedCallable(lambda x, scale=1.0: lin(x) * scale)
+    for i in range(3):
+        x = torch.randn(8, 64, device="cuda", dtype=torch.half)
+        torch.testing.assert_close(g(x, scale=2.0), lin(x) * 2.0)
+    assert len(g._graphs) == 1
+    g(torch.randn(4, 64, device="cuda", dtype=torch.half), scale=2.0)
+    assert len(g._graphs) == 2
+
+    class UNet(torch.nn.Module):
+        in_channels = 4
+
+        def __init__(self):
+            super().__init__()
+            self.conv = torch.nn.Conv2d(4, 4, 3, padding=1)
+
+        def forward(self, sample, t, ehs, return_dict=True):
+            return self.conv(sample) * t + ehs.mean()
+
+    u = DSUNet(UNet().cuda().half())
+    for i in range(2):
+        s, t, e = (torch.randn(1, 4, 16, 16, device="cuda", dtype=torch.half), torch.tensor(float(i + 1), device="cuda").half(),
+                   torch.randn(1, 7, 8, device="cuda", dtype=torch.half))
+        torch.testing.assert_close(u(s, t, e), u.unet(s, t, e), rtol=1e-2, atol=1e-2)
+    assert u.cuda_graph_created

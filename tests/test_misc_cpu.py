@@ -282,3 +282,89 @@ def test_small_utils():
     assert flat.tolist() == [4, 5] + list(range(10))
     mpl.lazy_init_hp_params_optimizer_state(ps[:2], flat, {flat: {"exp_avg": torch.arange(12.0), "step": torch.tensor(1)}})
     assert m1.get_hp_fragment("exp_avg").tolist() == list(range(2, 12))
+
+
+def test_diffusers_wrappers_cpu_passthrough():
+    """DSUNet / DSVAE / DSClipEncoder forward to the wrapped module (graphs engage only for CUDA tensors)."""
+    from hcache_deepspeed_b200.model_implementations.diffusers import DSUNet, DSVAE
+    from hcache_deepspeed_b200.model_implementations.features import GraphedCallable
+    from hcache_deepspeed_b200.model_implementations.transformers.clip_encoder import DSClipEncoder
+    from hcache_deepspeed_b200.module_inject.replace_module import generic_injection
+
+    class UNet(torch.nn.Module):
+        in_channels = 4
+
+        def __init__(self):
+            super().__init__()
+            self.conv = torch.nn.Conv2d(4, 4, 1)
+
+        def forward(self, sample, t, ehs, return_dict=True):
+            return self.conv(sample) + t + ehs.mean()
+
+    class VAE(torch.nn.Module):
+        def __init__(self):
+            super().__init__()
+            self.lin = torch.nn.Linear(4, 4)
+
+        def encode(self, x):
+            return self.lin(x)
+
+        def decode(self, z):
+            return self.lin(z) * 2
+
+        def forward(self, x):
+            return self.decode(self.encode(x))
+
+    pipe = types.SimpleNamespace(unet=UNet(), vae=VAE(), text_encoder=torch.nn.Linear(4, 4))
+    generic_injection(pipe, dtype=torch.float32, enable_cuda_graph=True)
+    assert isinstance(pipe.unet, DSUNet) and isinstance(pipe.vae, DSVAE) and isinstance(pipe.text_encoder, DSClipEncoder)
+    x = torch.randn(1, 4, 2, 2)
+    want = pipe.unet.unet(x, torch.tensor(1.0), torch.ones(3))
+    torch.testing.assert_close(pipe.unet(x, torch.tensor(1.0), torch.ones(3)), want)
+    assert pipe.unet.in_channels == 4 and not pipe.unet.cuda_graph_created
+    assert not any(p.requires_grad for p in pipe.unet.parameters())
+    z = torch.randn(2, 4)
+    torch.testing.assert_close(pipe.vae.decode(z), pipe.vae.vae.decode(z))
+    torch.testing.assert_close(pipe.vae(z), pipe.vae.vae(z))
+    torch.testing.assert_close(pipe.text_encoder(z), pipe.text_encoder.enc(z))
+    assert pipe.text_encoder.iter == 1
+    calls = []
+    g = GraphedCallable(lambda a, k=1: calls.append(k) or a * k)
+    assert g(torch.ones(2), k=3).tolist() == [3, 3] and calls == [3]
+
+
+def test_shim_packages_and_random_ltd_autograd():
+    import numpy as np
+    from hcache_deepspeed_b200.nebula import DeepSpeedNebulaConfig
+    from hcache_deepspeed_b200.ops.aio import AsyncIOHandle  # noqa: F401
+    from hcache_deepspeed_b200.ops.gds import gds_available
+    from hcache_deepspeed_b200.ops.random_ltd import GatherTokens, ScatterTokens, bert_sample_tokens, gpt_sample_tokens
+    from hcache_deepspeed_b200.pipe import LayerSpec, PipelineModule, TiedLayerSpec  # noqa: F401
+    from hcache_deepspeed_b200.runtime.compression import CupyBackend
+    assert isinstance(gds_available(), bool)
+    n = DeepSpeedNebulaConfig({"nebula": {"enabled": True, "persistent_storage_path": "/x"}})
+    assert n.enabled and n.persistent_storage_path == "/x" and n.persistent_time_interval == 100
+    b = CupyBackend()
+    bits = torch.rand(64) > 0.5
+    chunks = b.compress_by_chunk(bits, 2)
+    assert torch.cat(chunks).tolist() == np.packbits(bits.numpy()).tolist()
+    assert b.unpackbits(torch.cat(chunks)).bool().tolist() == bits.tolist()
+
+    torch.manual_seed(0)
+    idx, mask = gpt_sample_tokens(5, 12, 3, layers=2, attn_mask=torch.ones(3, 1, 12, 12))
+    assert idx.shape == (2, 3, 5) and idx.dtype == torch.int32 and mask.shape == (3, 1, 5, 5)
+    assert (idx[..., 1:] > idx[..., :-1]).all()
+    full_mask = torch.arange(3 * 12 * 12, dtype=torch.float32).reshape(3, 1, 12, 12)
+    bidx, bmasks = bert_sample_tokens(4, 12, 3, layers=1, attn_mask=full_mask)
+    r = bidx[0, 1].long()
+    assert torch.equal(bmasks[0][1, 0], full_mask[1, 0][r][:, r])
+    for batch_first in (True, False):
+        x = torch.randn(3, 12, 4, requires_grad=True) if batch_first else torch.randn(12, 3, 4, requires_grad=True)
+        _, part = GatherTokens.apply(x, idx[0], batch_first)
+        assert part.shape == ((3, 5, 4) if batch_first else (5, 3, 4))
+        out = ScatterTokens.apply(x, part * 2, idx[0], batch_first)
+        out.sum().backward()
+        kept = torch.zeros(3, 12)
+        kept.scatter_(1, idx[0].long(), 1.0)
+        want = (1 + kept)[:, :, None].expand(3, 12, 4)       # dropped tokens: identity; kept tokens: 2x path
+        torch.testing.assert_close(x.grad if batch_first else x.grad.transpose(0, 1), want)
