@@ -117,6 +117,15 @@ struct Operands {
     CUtensorMap ta, tw;
 };
 
+// ---- prefill-size M: CTA-pair kernel (gemm_2sm.cu) ------------------------------------------------------------
+int gemm_2sm_dispatch(const void* A, int64_t lda_bytes, const float* a_scale, const void* W, int64_t ldw_bytes,
+                      const float* w_scale, int M, int N, int K, bool fp8, bool bf16, int epilogue, int act, const void* bias,
+                      void* out, int64_t ldo, int bn, cudaStream_t stream);
+static bool pair_enabled() {
+    static const int on = getenv("HDS_GEMM_2SM") ? atoi(getenv("HDS_GEMM_2SM")) : 1;
+    return on != 0;
+}
+
 // ---- decode-size M: feature-major weight-streaming kernel (gemm_skinny.cuh) -------------------------------
 static inline int skinny_nt(int M) { return M <= 16 ? 16 : M <= 32 ? 32 : 64; }
 static bool skinny_enabled() {
@@ -279,6 +288,12 @@ extern "C" int hds_gemm(const void* A, int64_t lda, const void* W, int64_t ldw, 
     if (M <= 64 && ldw >= 0 && (bn == -1 || (bn == 0 && skinny_enabled() && (M <= 16 || epilogue == EPI_GATED))))
         return launch_skinny(epilogue, dtype == 0, A, lda, W, ldw, M, N, K, act, bias, out, ldo, nullptr, 0, splitk_ws,
                              splitk_ws_bytes, splits, static_cast<cudaStream_t>(stream));
+    // measured (profiles/kernel_bench_gemm_2sm.txt): with at least one full wave of 256 x 256 pair tiles the
+    // cta_group::2 kernel is 1.10-1.20x the single-CTA kernel and level with cuBLAS
+    if (bn == 0 && M > 128 && ldw >= 0 && pair_enabled() && lda % 8 == 0 && ldw % 8 == 0 && K % 8 == 0 &&
+        static_cast<int64_t>((M + 255) / 256) * ((N + 255) / 256) * 2 >= sm_count())
+        return hds::gemm_2sm_dispatch(A, lda * 2, nullptr, W, ldw * 2, nullptr, M, N, K, false, dtype == 0, epilogue, act, bias, out,
+                                 ldo, 256, static_cast<cudaStream_t>(stream));
     GemmArgs g;
     memset(&g, 0, sizeof(g));
     Operands ops;

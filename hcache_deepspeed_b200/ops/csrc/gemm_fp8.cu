@@ -221,6 +221,13 @@ static int launch_fp8_bn(int bn, const CUtensorMap& ta, const CUtensorMap& tw, c
 
 }  // namespace hds
 
+namespace hds {
+// gemm_2sm.cu: CTA-pair (cta_group::2) kernel shared by the 16-bit and fp8 operand kinds
+int gemm_2sm_dispatch(const void* A, int64_t lda_bytes, const float* a_scale, const void* W, int64_t ldw_bytes,
+                      const float* w_scale, int M, int N, int K, bool fp8, bool bf16, int epilogue, int act, const void* bias,
+                      void* out, int64_t ldo, int bn, cudaStream_t stream);
+}  // namespace hds
+
 using namespace hds;
 
 extern "C" int hds_quantize_fp8_rows(const void* x, int64_t ldx, int rows, int K, int dtype, void* q, int64_t ldq,
@@ -245,6 +252,10 @@ extern "C" int hds_gemm_fp8(const void* Aq, int64_t lda, const float* a_scale, c
     HDS_REQUIRE(out_dtype == 0 || out_dtype == 1, "hds_gemm_fp8: out dtype must be 0 (bf16) or 1 (fp16)");
     HDS_REQUIRE(epilogue != EPI_GATED || (N % 2 == 0), "hds_gemm_fp8: gated epilogue needs an even N");
     HDS_REQUIRE(M > 0 && N > 0 && K > 0 && K % 16 == 0, "hds_gemm_fp8: K must be a positive multiple of 16");
+    // bn: 0 = auto (CTA-pair kernel above one m-tile), 64 / 128 / 256 = single-CTA tile, 1128 / 1256 = CTA-pair tile
+    if ((bn == 0 && M > 128) || bn > 1000)
+        return gemm_2sm_dispatch(Aq, lda, a_scale, Wq, ldw, w_scale, M, N, K, true, out_dtype == 0, epilogue, act, bias, out,
+                                 ldo, bn > 1000 ? bn - 1000 : 0, static_cast<cudaStream_t>(stream));
     if (bn <= 0) {
         // widest tile that still gives every SM work; decode-size problems take the narrow tile for more CTAs
         const int64_t m_tiles = (M + 127) / 128;

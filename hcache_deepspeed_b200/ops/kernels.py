@@ -396,6 +396,22 @@ def moe_gemm(a: torch.Tensor, w_stacked: torch.Tensor, pad_off: torch.Tensor, n_
     return out
 
 
+def gemm_2sm(a: torch.Tensor, w: torch.Tensor, out: Optional[torch.Tensor] = None, bias: Optional[torch.Tensor] = None,
+             act: int = ACT_IDENTITY, gated: bool = False, bn: int = 0) -> torch.Tensor:
+    """``out = epilogue(a @ w.T + bias)`` on the CTA-pair kernel (``tcgen05.mma.cta_group::2``: two SMs per 256 x bn tile)."""
+    _check_2d(a, "a")
+    _check_2d(w, "w")
+    M, K = a.shape
+    N = w.shape[0]
+    if out is None:
+        out = torch.empty(M, N // 2 if gated else N, dtype=a.dtype, device=a.device)
+    rc = native.cuda_lib().hds_gemm_2sm(_p(a), a.stride(0), _p(w), w.stride(0), M, N, K, _dt(a),
+                                        EPI_GATED if gated else EPI_STORE, act, _p(bias), _p(out), out.stride(0), bn, _stream())
+    native.check(rc, "hds_gemm_2sm")
+    _count()
+    return out
+
+
 def quantize_fp8_rows(x: torch.Tensor, q: Optional[torch.Tensor] = None,
                       scales: Optional[torch.Tensor] = None) -> Tuple[torch.Tensor, torch.Tensor]:
     """Row-wise E4M3 quantisation: ``q[r] = e4m3(x[r] / scales[r])`` with ``scales[r] = amax(x[r]) / 448``.

@@ -55,6 +55,7 @@ def _declare_cuda(lib: ctypes.CDLL) -> None:
         "hds_moe_scatter": [P, L, P, L, P, P, P, P, P, I, I, I, I, P],
         "hds_moe_gemm": [P, L, P, L, P, I, I, I, I, I, I, I, P, L, P],
         "hds_moe_gather": [P, L, P, P, P, L, I, I, I, I, P],
+        "hds_gemm_2sm": [P, L, P, L, I, I, I, I, I, I, P, P, L, I, P],
         "hds_quantize_fp8_rows": [P, L, I, I, I, P, L, P, P],
         "hds_gemm_fp8": [P, L, P, P, L, P, I, I, I, I, I, I, P, P, L, I, P],
         "hds_quantize_int": [P, I, L, I, I, I, P, P, P],

@@ -225,6 +225,12 @@ int hds_gemm_fp8(const void* Aq, int64_t lda, const float* a_scale, const void* 
                  int M, int N, int K, int out_dtype, int epilogue, int act, const void* bias, void* out, int64_t ldo,
                  int bn, void* stream);
 
+/* CTA-pair GEMM (tcgen05 cta_group::2, 256 x bn tiles over two SMs): out = epilogue(A W^T + bias), 16-bit operands.
+ * Arguments as hds_gemm (no split-K); bn: 0 = auto, 128 or 256. hds_gemm_fp8 reaches the same kernel with bn = 0
+ * (auto, M > 128) or bn = 1128 / 1256. */
+int hds_gemm_2sm(const void* A, int64_t lda, const void* W, int64_t ldw, int M, int N, int K, int dtype, int epilogue,
+                 int act, const void* bias, void* out, int64_t ldo, int bn, void* stream);
+
 /* ---- group-wise quantizers (ref: csrc/quantization, csrc/fp_quantizer) ------------------------------------ */
 /* dtype codes: 0 bf16, 1 fp16, 2 fp32. Integer: bits 4 or 8; params[g] = (scale, offset): value = code * scale + offset.
  * 4-bit codes are packed two per byte (low nibble first). */

@@ -436,3 +436,17 @@ def test_moe_pipeline(T, E, k, norm):
             y = ref.gemm(h, w_down[e * H:(e + 1) * H], out_dtype=torch.float32).to(x.dtype)
             want[t] += float(scores[t, j]) * y[0].float()
     torch.testing.assert_close(out, want, rtol=3e-2, atol=3e-2)
+
+
+@pytest.mark.parametrize("dtype", DTYPES)
+@pytest.mark.parametrize("M,N,K_", [(130, 512, 64), (256, 256, 128), (300, 1000, 2096), (1024, 4096, 1024), (4100, 1376, 512)])
+@pytest.mark.parametrize("bn", [0, 128, 256])
+@pytest.mark.parametrize("mode", ["store", "gated"])
+def test_gemm_2sm(dtype, M, N, K_, bn, mode):
+    """CTA-pair kernel (tcgen05 cta_group::2, 256 x bn tiles): ragged M / N / K, both tile widths, both epilogues."""
+    torch.manual_seed(M)
+    a, w, b = rand(M, K_, dtype=dtype), rand(N, K_, dtype=dtype, scale=K_ ** -0.5), rand(N, dtype=dtype)
+    gated = mode == "gated"
+    out = K().gemm_2sm(a, w, bias=b, act=3 if gated else 2, gated=gated, bn=bn)
+    want = ref.gemm(a, w, bias=b, act=3 if gated else 2, gated=gated, out_dtype=torch.float32)
+    torch.testing.assert_close(out.float(), want, **tol(dtype))

@@ -65,6 +65,8 @@ def bench_gemm():
         for bn in (128, 256):
             med, mn = timeit(lambda: K.gemm(a, w, out=out, bn=bn))
             report(f"gemm_store M{M} N{N} K{Kd} bn{bn}", med, mn, flops=2.0 * M * N * Kd)
+        med, mn = timeit(lambda: K.gemm_2sm(a, w, out=out, bn=256))
+        report(f"gemm_2sm_store M{M} N{N} K{Kd} bn256", med, mn, flops=2.0 * M * N * Kd)
         med, mn = timeit(lambda: torch.matmul(a, w.t(), out=out))
         report(f"cublas M{M} N{N} K{Kd}", med, mn, flops=2.0 * M * N * Kd)
     # gated up-projection (Llama-2-7B: I=11008)
@@ -73,6 +75,8 @@ def bench_gemm():
     out = torch.empty(M, N // 2, device=dev, dtype=torch.bfloat16)
     med, mn = timeit(lambda: K.gemm(a, w, act=3, gated=True, out=out, bn=256))
     report(f"gemm_gated M{M} N{N} K{Kd} bn256", med, mn, flops=2.0 * M * N * Kd)
+    med, mn = timeit(lambda: K.gemm_2sm(a, w, act=3, gated=True, out=out, bn=256))
+    report(f"gemm_2sm_gated M{M} N{N} K{Kd} bn256", med, mn, flops=2.0 * M * N * Kd)
 
 
 def bench_decode_gemm():
@@ -211,9 +215,9 @@ def bench_gemm_fp8():
         aq, a_s = K.quantize_fp8_rows(a)
         wq, w_s = K.quantize_fp8_rows(w)
         out = torch.empty(M, N, device=dev, dtype=torch.bfloat16)
-        for bn in (128, 256):
+        for bn in (128, 256, 1256):
             med, mn = timeit(lambda: K.gemm_fp8(aq, a_s, wq, w_s, out, bn=bn))
-            report(f"gemm_fp8 M{M} N{N} K{Kd} bn{bn}", med, mn, flops=2.0 * M * N * Kd)
+            report(f"gemm_fp8{'_2sm' if bn > 1000 else ''} M{M} N{N} K{Kd} bn{bn % 1000}", med, mn, flops=2.0 * M * N * Kd)
         med, mn = timeit(lambda: K.quantize_fp8_rows(a, aq, a_s))
         report(f"quantize_fp8_rows M{M} K{Kd}", med, mn, bytes_=M * Kd * 3)
         med, mn = timeit(lambda: K.gemm(a, w, out=out, bn=256))

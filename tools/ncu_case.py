@@ -53,6 +53,13 @@ elif case == "gemm":
     a, w = rand(M, Kd), rand(N, Kd, scale=Kd ** -0.5)
     out = torch.empty(M, N, device=dev, dtype=torch.bfloat16)
     fn = lambda: K.gemm(a, w, out=out, bn=256)
+elif case == "gemm_fp8":
+    M, N, Kd = 4096, 12288, 4096
+    a, w = rand(M, Kd), rand(N, Kd, scale=Kd ** -0.5)
+    aq, a_s = K.quantize_fp8_rows(a)
+    wq, w_s = K.quantize_fp8_rows(w)
+    out = torch.empty(M, N, device=dev, dtype=torch.bfloat16)
+    fn = lambda: K.gemm_fp8(aq, a_s, wq, w_s, out, bn=256)
 elif case == "restore":
     T, H, n_kv, d, bs = 4096, 4096, 32, 128, 64
     lat = rand(T, H)
