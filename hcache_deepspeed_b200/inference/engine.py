@@ -72,7 +72,12 @@ class InferenceEngine(torch.nn.Module):
         if config.tensor_parallel.tp_size > 1:
             self._create_model_parallel_group(config)
         self.injected = bool(config.replace_with_kernel_inject or config.hcache.enabled)
-        if self.injected:
+        self.fused_layers = 0
+        if self.injected and not config.hcache.enabled and not self._has_v2_policy():
+            # families outside the ragged executor: per-layer injection of the v1 fused layer
+            self.injected = False
+            self._apply_v1_injection(config)
+        elif self.injected:
             self._apply_injection()
         else:
             if config.tensor_parallel.tp_size > 1:
@@ -105,6 +110,27 @@ class InferenceEngine(torch.nn.Module):
     def _convert_to_dtype(self, config) -> None:
         if config.dtype in (torch.half, torch.bfloat16, torch.float32):
             self.module.to(config.dtype)
+
+    def _has_v2_policy(self) -> bool:
+        from .v2.model_implementations import MODEL_TYPE_TO_POLICY
+        return getattr(getattr(self.module, "config", None), "model_type", None) in MODEL_TYPE_TO_POLICY
+
+    def _apply_v1_injection(self, config) -> None:
+        """``replace_with_kernel_inject`` for a family without a ragged-executor policy: swap every block for the fused
+        layer through its container policy (``module_inject/containers``; ref ``replace_module.py:210-265``)."""
+        from ..module_inject.containers import inject_fused_layers
+        self._convert_to_dtype(config)
+        tp = config.tensor_parallel.tp_size
+        rank = torch.distributed.get_rank(self.inference_mp_group) if tp > 1 else 0
+        self.fused_layers = inject_fused_layers(self.module, dtype=config.dtype, mp_size=tp, mp_rank=rank,
+                                                mp_group=self.inference_mp_group if tp > 1 else None,
+                                                max_out_tokens=getattr(config, "max_out_tokens", 1024))
+        if self.fused_layers == 0:
+            mt = getattr(getattr(self.module, "config", None), "model_type", None)
+            raise ValueError(f"kernel injection is not available for model type {mt}: no ragged-executor policy and no "
+                             f"container policy matches its blocks")
+        self.module.to(self.device)
+        log_dist(f"init_inference: {self.fused_layers} transformer blocks replaced by the fused inference layer", [0])
 
     def _apply_injection(self) -> None:
         from .v2.checkpoint import InMemoryModelEngine

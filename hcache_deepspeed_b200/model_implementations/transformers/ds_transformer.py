@@ -35,7 +35,8 @@ class DeepSpeedSelfAttention(nn.Module):
         self.attn_ob = nn.Parameter(torch.zeros(h, dtype=dt), requires_grad=False)
         self.norm_factor = math.sqrt(math.sqrt(self.head_dim)) ** -1 if c.scale_attention else 1.0
         if c.scale_attn_by_inverse_layer_idx:
-            self.norm_factor *= math.sqrt(c.layer_id + 1) ** -0.5
+            # scores are multiplied by norm_factor ** 2: an extra 1 / (layer index + 1), index counted within the model
+            self.norm_factor *= (getattr(c, "layer_index", c.layer_id) + 1) ** -0.5
 
     def forward(self, x, input_mask=None, norm_w=None, norm_b=None, alibi=None, is_prompt: Optional[bool] = None):
         c = self.config
@@ -69,11 +70,11 @@ class DeepSpeedMLP(nn.Module):
         self.output_w = nn.Parameter(torch.empty(inter, h, dtype=dt), requires_grad=False)
         self.output_b = nn.Parameter(torch.zeros(h, dtype=dt), requires_grad=False)
 
-    def forward(self, attn_out, residual, attn_bias):
+    def forward(self, attn_out, residual, attn_bias, skip_norm: bool = False):
         c = self.config
         out, res_add = self.ops.mlp_gemm(attn_out, residual, attn_bias, self.inter_w, self.output_w, self.inter_b, self.attn_nw,
                                          self.attn_nb, c.layer_norm_eps, c.pre_layer_norm, c.mlp_after_attn,
-                                         act=c.mlp_act_func_type, rms_norm=c.norm_type == "rms_norm")
+                                         act=c.mlp_act_func_type, rms_norm=c.norm_type == "rms_norm", skip_norm=skip_norm)
         if c.mp_size > 1 and dist.is_initialized() and self.mp_group is not None:
             dist.all_reduce(out, group=self.mp_group)
         return out, res_add
@@ -122,14 +123,21 @@ class DeepSpeedTransformerInference(nn.Module):
         mask = input_mask if input_mask is not None else (attention_mask if attention_mask is not None else attn_mask)
         get_present = get_present or get_key_value or use_cache
         c = self.config
-        attn_out, k, v, ctx, _ = self.attention(input, mask, self.norm_w, self.norm_b, alibi,
-                                                is_prompt=(layer_past is None and past_key_value is None) or input.shape[1] > 1)
-        mlp_out, res_add = self.mlp(attn_out, input, self.attention.attn_ob)
-        ops = self.mlp.ops
-        out = ops.residual_add_bias(mlp_out, res_add, attn_out, self.attention.attn_ob, self.mlp.output_b, c.mp_size,
-                                    c.mlp_after_attn, True, c.pre_layer_norm)
-        if not c.pre_layer_norm:
-            out = ops.layer_norm(out, self.norm_w, self.norm_b, c.layer_norm_eps)
+        attn_out, k, v, ctx, normed = self.attention(input, mask, self.norm_w, self.norm_b, alibi,
+                                                     is_prompt=kwargs.get("is_prompt", (layer_past is None and past_key_value is None)
+                                                                          or input.shape[1] > 1))
+        ob, fb = self.attention.attn_ob, self.mlp.output_b
+        if c.mlp_after_attn:
+            # sequential: h = x + attn(x); out = h + mlp(norm(h))   (post-LN: norms sit after each residual add instead)
+            mlp_out, res_add = self.mlp(attn_out, input, ob)
+            out = mlp_out + res_add + fb
+            if not c.pre_layer_norm:
+                out = self.mlp.ops.layer_norm(out, self.norm_w, self.norm_b, c.layer_norm_eps)
+        else:
+            # parallel: out = x + attn(norm1(x)) + mlp(norm2(x)); one shared norm when the MLP has none of its own (GPT-J)
+            own_norm = getattr(self.mlp, "has_own_norm", True)
+            mlp_out, _ = self.mlp(input if own_norm else normed, None, None, skip_norm=not own_norm)
+            out = input + attn_out + ob + mlp_out + fb
         if get_present:
             return (out, (k, v))
         return (out, ) if c.return_tuple else out

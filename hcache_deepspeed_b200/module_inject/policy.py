@@ -4,7 +4,8 @@ The reference keeps one container + policy class per family under ``module_injec
 distil_bert, gpt2, gptj, gptneo, gptneox, internlm, llama, llama2, megatron_gpt, megatron_gpt_moe, opt, unet, vae) that
 extract q/k/v/o/mlp/norm tensors from one HF block. Here the per-family knowledge lives in
 ``models/families.py`` (name mappers) + ``models/arch.py`` (ArchSpec builders); a policy is just the pair. Families
-without a mapper fall back to AutoTP.
+without a mapper get per-layer injection of the v1 fused layer through ``module_inject/containers`` (gpt2, gptj, gptneo,
+gptneox, bloom, opt, bert, distil_bert) or fall back to AutoTP.
 """
 from __future__ import annotations
 
@@ -30,10 +31,10 @@ def _table() -> Dict[str, InjectionPolicy]:
         InjectionPolicy("falcon", ("falcon", ), True), InjectionPolicy("phi", ("phi", ), True),
         InjectionPolicy("phi3", ("phi3", ), True), InjectionPolicy("qwen", ("qwen", ), True),
         InjectionPolicy("qwen2", ("qwen2", ), True), InjectionPolicy("qwen2_moe", ("qwen2_moe", ), True),
-        InjectionPolicy("gpt2", ("gpt2", ), False, "AutoTP (Conv1D blocks are converted to Linear first)"),
-        InjectionPolicy("gptj", ("gptj", ), False, "AutoTP"), InjectionPolicy("gptneo", ("gpt_neo", ), False, "AutoTP"),
-        InjectionPolicy("gptneox", ("gpt_neox", ), False, "AutoTP"), InjectionPolicy("bloom", ("bloom", ), False, "AutoTP"),
-        InjectionPolicy("bert", ("bert", ), False, "AutoTP"), InjectionPolicy("distil_bert", ("distilbert", ), False, "AutoTP"),
+        InjectionPolicy("gpt2", ("gpt2", ), False, "v1 fused layer (module_inject/containers) or AutoTP"),
+        InjectionPolicy("gptj", ("gptj", ), False, "v1 fused layer or AutoTP"), InjectionPolicy("gptneo", ("gpt_neo", ), False, "v1 fused layer or AutoTP"),
+        InjectionPolicy("gptneox", ("gpt_neox", ), False, "v1 fused layer or AutoTP"), InjectionPolicy("bloom", ("bloom", ), False, "v1 fused layer or AutoTP"),
+        InjectionPolicy("bert", ("bert", ), False, "v1 fused layer or AutoTP"), InjectionPolicy("distil_bert", ("distilbert", ), False, "v1 fused layer or AutoTP"),
         InjectionPolicy("megatron_gpt", ("megatron-gpt", ), False, "AutoTP"),
         InjectionPolicy("megatron_gpt_moe", ("megatron-gpt-moe", ), False, "AutoTP + moe.MoE"),
         InjectionPolicy("clip", ("clip", ), False, "generic_injection"), InjectionPolicy("unet", ("unet", ), False, "generic_injection"),

@@ -153,19 +153,28 @@ class InferenceOps:
 
     @staticmethod
     def mlp_gemm(x, residual, input_bias, weight_interm, weight_out, bias, gamma, beta, eps, pre_layer_norm: bool,
-                 mlp_after_attn: bool, act: str = "gelu", transposed_mode: bool = False, rms_norm: bool = False):
-        """Post-attention norm + MLP-1 (+bias, activation) + MLP-2. Returns (output, residual-added input)."""
+                 mlp_after_attn: bool, act: str = "gelu", transposed_mode: bool = False, rms_norm: bool = False,
+                 skip_norm: bool = False):
+        """Norm + MLP-1 (+bias, activation) + MLP-2. Sequential wiring (``mlp_after_attn``): the norm input is
+        ``x + residual + input_bias`` (attention output + layer input). Parallel wiring: ``x`` is normed as given
+        (``skip_norm``: ``x`` is already the normed layer input, GPT-J). Returns (output, tensor the MLP output is added
+        to: the un-normed sum for pre-LN blocks, the normed one for post-LN blocks)."""
         res_add = x + residual + (input_bias if input_bias is not None else 0) if mlp_after_attn else x
-        if rms_norm:
+        if skip_norm:
+            normed = res_add
+        elif rms_norm:
             normed = InferenceOps.rms_norm(res_add, gamma, eps)
         else:
-            normed = F.layer_norm(res_add, x.shape[-1:], gamma, beta, eps) if mlp_after_attn or pre_layer_norm else res_add
+            normed = F.layer_norm(res_add, x.shape[-1:], gamma, beta, eps)
         w1 = weight_interm if transposed_mode else weight_interm.t()
         w2 = weight_out if transposed_mode else weight_out.t()
         h = F.linear(normed, w1, bias)
-        h = {"gelu": F.gelu, "relu": F.relu, "silu": F.silu}.get(act, F.gelu)(h) if act not in ("gated_gelu", "gated_silu") \
-            else InferenceOps.gated_activation(h, None, act.split("_")[1])
-        return F.linear(h, w2), res_add
+        if act in ("gated_gelu", "gated_silu"):
+            h = InferenceOps.gated_activation(h, None, act.split("_")[1])
+        else:
+            h = {"gelu": F.gelu, "relu": F.relu, "silu": F.silu,
+                 "gelu_new": lambda t: F.gelu(t, approximate="tanh")}.get(act, F.gelu)(h)
+        return F.linear(h, w2), (res_add if pre_layer_norm or not mlp_after_attn else normed)
 
     # ---- attention ---------------------------------------------------------------------------------------------
     def softmax_context(self, qkv: torch.Tensor, attn_mask: Optional[torch.Tensor], rotary_dim: int, rotate_half: bool,
