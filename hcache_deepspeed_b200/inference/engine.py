@@ -71,6 +71,8 @@ class InferenceEngine(torch.nn.Module):
             else torch.device("cpu")
         if config.tensor_parallel.tp_size > 1:
             self._create_model_parallel_group(config)
+        if config.checkpoint is not None:
+            self._load_checkpoint(config.checkpoint, base_dir=config.base_dir)
         self.injected = bool(config.replace_with_kernel_inject or config.hcache.enabled)
         self.fused_layers = 0
         if self.injected and not config.hcache.enabled and not self._has_v2_policy():
@@ -86,6 +88,13 @@ class InferenceEngine(torch.nn.Module):
                              self.inference_mp_group)
             self._convert_to_dtype(config)
             self.module.to(self.device)
+        if config.save_mp_checkpoint_path:
+            from ..module_inject.load_checkpoint import save_mp_checkpoint
+            tp = config.tensor_parallel.tp_size
+            rank = torch.distributed.get_rank(self.inference_mp_group) if tp > 1 else 0
+            save_mp_checkpoint(self.module, config.save_mp_checkpoint_path, tp, rank,
+                               model_type=getattr(getattr(self.module, "config", None), "model_type", "ds_model"),
+                               dtype=config.dtype)
         if hasattr(self.module, "generate"):
             self._orig_generate = self.module.generate
         if config.tensor_parallel.tp_size > 1 and on_gpu:
@@ -110,6 +119,16 @@ class InferenceEngine(torch.nn.Module):
     def _convert_to_dtype(self, config) -> None:
         if config.dtype in (torch.half, torch.bfloat16, torch.float32):
             self.module.to(config.dtype)
+
+    def _load_checkpoint(self, load_dir, base_dir: str = "", load_module_strict: bool = False, tag=None) -> None:
+        """``init_inference(model, checkpoint=...)``: a checkpoint json (path or dict), a folder of weight files, or a
+        DeepSpeed / Megatron ``mp_rank_*`` folder (merged or split to this TP degree); meta-device modules are
+        materialised by the load (ref ``inference/engine.py:411-468``)."""
+        from ..module_inject.load_checkpoint import load_checkpoint_into
+        tp = self._config.tensor_parallel.tp_size
+        rank = torch.distributed.get_rank(self.inference_mp_group) if tp > 1 and self.inference_mp_group is not None else 0
+        n = load_checkpoint_into(self.module, load_dir, base_dir or "", tp_size=tp, tp_rank=rank, strict=load_module_strict, tag=tag)
+        log_dist(f"init_inference: loaded {n} checkpoint file(s)", [0])
 
     def _has_v2_policy(self) -> bool:
         from .v2.model_implementations import MODEL_TYPE_TO_POLICY

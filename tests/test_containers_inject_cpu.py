@@ -110,3 +110,40 @@ def test_tensor_parallel_slices_sum_to_the_full_layer():
                                        lay.mlp.attn_nw, lay.mlp.attn_nb, 1e-5, True, True, act="gelu_new")[0] for lay, _ in parts)
         got = h + mlp + parts[0][0].mlp.output_b
     torch.testing.assert_close(got, want, rtol=1e-4, atol=1e-5)
+
+
+def test_checkpoint_json_into_meta_model_then_inject(tmp_path):
+    """init_inference(meta model, checkpoint=json): weights come from sharded files, blocks are injected afterwards;
+    save_mp_checkpoint_path writes a reloadable per-rank checkpoint (ref: inference/engine.py:366-475)."""
+    import json
+    torch.manual_seed(0)
+    cfg = CAUSAL["gpt2"]()
+    src = AutoModelForCausalLM.from_config(cfg).eval().float()
+    ids = torch.randint(1, 50, (1, 6))
+    with torch.no_grad():
+        want = src(ids).logits
+    sd = {k: v for k, v in src.state_dict().items() if k != "lm_head.weight"}        # tied to wte
+    keys = sorted(sd)
+    torch.save({k: sd[k] for k in keys[::2]}, tmp_path / "part0.pt")
+    torch.save({k: sd[k] for k in keys[1::2]}, tmp_path / "part1.pt")
+    (tmp_path / "ckpt.json").write_text(json.dumps({"type": "ds_model", "checkpoints": ["part0.pt", "part1.pt"], "version": 1.0}))
+    with torch.device("meta"):
+        meta_model = AutoModelForCausalLM.from_config(cfg).eval()
+    assert next(meta_model.parameters()).is_meta
+    out_dir = tmp_path / "mp"
+    engine = ds.init_inference(meta_model, dtype=torch.float32, replace_with_kernel_inject=True, checkpoint=str(tmp_path / "ckpt.json"),
+                               base_dir=str(tmp_path), save_mp_checkpoint_path=str(out_dir))
+    assert engine.fused_layers == 2
+    with torch.no_grad():
+        torch.testing.assert_close(engine(ids).logits, want, rtol=1e-4, atol=1e-5)
+    saved = json.loads((out_dir / "ds_inference_config.json").read_text())
+    assert saved["checkpoints"]["tp"] == ["tp_00_00.pt"] and (out_dir / "tp_00_00.pt").exists()
+
+    # a plain folder of weight files loads too
+    plain = AutoModelForCausalLM.from_config(cfg).eval().float()
+    folder = tmp_path / "w"
+    folder.mkdir()
+    torch.save(sd, folder / "pytorch_model.bin")
+    eng2 = ds.init_inference(plain, dtype=torch.float32, checkpoint=str(folder))
+    with torch.no_grad():
+        torch.testing.assert_close(eng2(ids).logits, want, rtol=1e-4, atol=1e-5)
