@@ -121,3 +121,36 @@ def test_v1_fused_layer_incremental_decode_matches_full_forward():
     q_k = ops.apply_rotary_pos_emb(torch.randn(1, 2, 3, 8), torch.randn(1, 2, 3, 8), 8, 0, 2, True)
     assert q_k[0].shape == (1, 2, 3, 8)
     DeepSpeedTransformerInference.release()
+
+
+def test_moe_inference_layer_matches_dense_evaluation():
+    """DeepSpeedMoEInference: top-k routed experts (+ residual PR-MoE blend) equal evaluating every expert densely."""
+    import torch.nn.functional as F
+    from hcache_deepspeed_b200.ops.transformer.inference.moe_inference import DeepSpeedMoEInference, DeepSpeedMoEInferenceConfig
+    torch.manual_seed(0)
+    for mlp_type, k in (("standard", 1), ("standard", 2), ("residual", 2)):
+        cfg = DeepSpeedMoEInferenceConfig(hidden_size=32, intermediate_size=64, heads=4, num_hidden_layers=1, layer_norm_eps=1e-5,
+                                          moe_experts=4, global_experts=4, k=k, mlp_type=mlp_type, return_tuple=False)
+        layer = DeepSpeedMoEInference(cfg)
+        for p in layer.parameters():
+            if p.dim() > 1:
+                torch.nn.init.normal_(p, std=0.2)
+        x = torch.randn(2, 6, 32)
+        out = layer(x)
+        # oracle
+        attn_out, _, _, _, _ = layer.attention(x, None, layer.norm_w, layer.norm_b, is_prompt=True)
+        res = x + attn_out + layer.attention.attn_ob
+        flat = F.layer_norm(res, (32, ), layer.attn_nw, layer.attn_nb, 1e-5).reshape(-1, 32)
+        probs = torch.softmax(flat @ layer.gate_w.t(), dim=-1)
+        top_p, top_e = probs.topk(k, dim=-1)
+        if k > 1:
+            top_p = top_p / top_p.sum(-1, keepdim=True)
+        dense = torch.stack([e(flat) for e in layer.mlp], dim=1)                      # [tokens, experts, hidden]
+        weights = torch.zeros_like(probs).scatter_(1, top_e, top_p)
+        moe = (dense * weights[:, :, None]).sum(dim=1)
+        if mlp_type == "residual":
+            coef = torch.softmax(flat @ layer.res_coef, dim=-1)
+            moe = layer.res_mlp(flat) * coef[:, 0:1] + moe * coef[:, 1:2]
+        torch.testing.assert_close(out, res + moe.view_as(res), rtol=1e-4, atol=1e-5)
+    y, (kk, vv) = layer(x, use_cache=True)
+    assert kk.shape[2] == 6
