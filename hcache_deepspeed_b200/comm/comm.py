@@ -267,7 +267,12 @@ def all_reduce(tensor, op=ReduceOp.SUM, group=None, async_op=False):
 @timed_op
 def inference_all_reduce(tensor, op=ReduceOp.SUM, group=None):
     """Latency-oriented all-reduce of the inference path (ref: comm.py:506). On CUDA this is NCCL (NVLS when
-    the switch offers it); the engine's own hot path bypasses it with fused GEMM epilogues."""
+    the switch offers it); the engine's own hot path bypasses it with fused GEMM epilogues. CPU fp32 / bf16 tensors
+    go through the shared-memory engine once ``comm.shm.attach(group)`` has been called (ref: torch.py:160-166)."""
+    if tensor.device.type == "cpu" and op == ReduceOp.SUM:
+        from . import shm
+        if shm.usable(tensor, group):
+            return shm.attached(group).all_reduce(tensor)
     return tdist.all_reduce(tensor, op=_op(op), group=group, async_op=False)
 
 

@@ -89,8 +89,8 @@ def build_host(force: bool = False, verbose: bool = False) -> Path:
     if force or _newer([*sources, *headers], HOST_LIB):
         if verbose:
             print("[hds build] compiling host runtime", file=sys.stderr)
-        _run(["g++", "-O2", "-std=c++17", "-fPIC", "-shared", "-pthread", "-I", str(REPO_INCLUDE), "-o", str(HOST_LIB),
-              *map(str, sources)])
+        _run(["g++", "-O2", "-ftree-vectorize", "-std=c++17", "-fPIC", "-shared", "-pthread", "-I", str(REPO_INCLUDE), "-o", str(HOST_LIB),
+              *map(str, sources), "-lrt"])
     return HOST_LIB
 
 

@@ -55,3 +55,9 @@ def declare(lib: ctypes.CDLL) -> None:
     lib.hds_cpu_adagrad_step.restype = I
     lib.hds_cpu_lion_step.argtypes = [P, P, P, L, F, F, F, F, P, I, I]
     lib.hds_cpu_lion_step.restype = I
+    lib.hds_shm_open.argtypes = [ctypes.c_char_p, I, I, L]
+    lib.hds_shm_open.restype = P
+    lib.hds_shm_allreduce.argtypes = [P, P, L, I]
+    lib.hds_shm_allreduce.restype = I
+    lib.hds_shm_close.argtypes = [P, I]
+    lib.hds_shm_close.restype = None

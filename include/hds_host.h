@@ -84,6 +84,14 @@ int hds_cpu_adagrad_step(float* params, const float* grads, float* exp_avg_sq, i
 int hds_cpu_lion_step(float* params, const float* grads, float* exp_avg, int64_t n, float lr, float beta1, float beta2,
                       float weight_decay, void* copy_out, int copy_dtype, int threads);
 
+/* ---- shared-memory all-reduce for intra-node CPU tensor parallelism (ref: csrc/cpu/comm/shm.cpp) ----------------
+ * hds_shm_open: every rank of the group maps POSIX segment "/<name>" (world slots of slot_bytes) and waits until all
+ * ranks have attached; NULL on failure. hds_shm_allreduce: in-place SUM over the group, dtype 0 = bf16 (fp32
+ * accumulation), 2 = fp32; any numel (chunked by slot size). hds_shm_close unmaps (one rank passes unlink_segment). */
+void* hds_shm_open(const char* name, int rank, int world, int64_t slot_bytes);
+int hds_shm_allreduce(void* handle, void* data, int64_t numel, int dtype);
+void hds_shm_close(void* handle, int unlink_segment);
+
 #ifdef __cplusplus
 }
 #endif

@@ -133,3 +133,32 @@ def onebit_adam_worker(rank, world):
         losses.append(float(loss.detach()))
     return {"losses": losses, "frozen": engine.basic_optimizer.adam_freeze_key, "allreduce_off": not engine.enable_backward_allreduce,
             "w": engine.module.head.weight.detach().clone()}
+
+
+def shm_allreduce_worker(rank, world):
+    """Shared-memory all-reduce (C++ engine) against gloo, through comm.inference_all_reduce."""
+    import hcache_deepspeed_b200 as ds
+    from hcache_deepspeed_b200 import comm as dist
+    from hcache_deepspeed_b200.comm import shm
+    ds.init_distributed(dist_backend="gloo")
+    g = shm.attach(slot_bytes=4096)                  # small slots: large tensors exercise the chunked path
+    out = {}
+    for dtype, n in ((torch.float32, 7), (torch.float32, 5000), (torch.bfloat16, 3001)):
+        torch.manual_seed(100 + rank)
+        x = torch.randn(n).to(dtype)
+        want = x.clone()
+        torch.distributed.all_reduce(want)           # gloo
+        got = x.clone()
+        assert shm.usable(got)
+        dist.inference_all_reduce(got)
+        out[f"{dtype}_{n}"] = float((got.float() - want.float()).abs().max())
+    for i in range(50):                              # back-to-back rounds: slot reuse must not race
+        t = torch.full((1500, ), float(rank + i))
+        dist.inference_all_reduce(t)
+        assert float(t[0]) == sum(r + i for r in range(world)) and float(t[-1]) == float(t[0])
+    y = torch.ones(4, dtype=torch.int32)             # unsupported dtype falls back to torch.distributed
+    dist.inference_all_reduce(y)
+    out["int_fallback"] = int(y[0])
+    out["name"] = g.name
+    shm.detach()
+    return out

@@ -88,3 +88,15 @@ def test_sequence_parallel_cross_entropy_single_rank():
     l2 = logits.detach().clone().requires_grad_(True)
     torch.nn.functional.cross_entropy(l2.reshape(-1, 11), tgt.reshape(-1), reduction="sum").backward()
     torch.testing.assert_close(logits.grad, l2.grad, rtol=1e-5, atol=1e-6)
+
+
+@pytest.mark.parametrize("world", [2, 3])
+def test_shm_allreduce_matches_gloo(world):
+    import os
+    from tests.parallel_helper import shm_allreduce_worker
+    res = run_distributed(shm_allreduce_worker, world)
+    for r in res:
+        assert r["torch.float32_7"] < 1e-6 and r["torch.float32_5000"] < 1e-5
+        assert r["torch.bfloat16_3001"] < 0.07        # one bf16 rounding of an fp32 sum vs gloo's pairwise bf16 adds
+        assert r["int_fallback"] == world
+    assert len({r["name"] for r in res}) == 1 and not os.path.exists("/dev/shm/" + res[0]["name"])
