@@ -45,7 +45,7 @@ def _mk(name, lib, symbols, doc=""):
     return type(name, (OpBuilder, ), {"NAME": name, "LIB": lib, "SYMBOLS": tuple(symbols), "__doc__": doc})
 
 
-InferenceCoreBuilder = _mk("inference_core_ops", "cuda", ["hds_gemm", "hds_norm"])
+InferenceCoreBuilder = _mk("inference_core_ops", "cuda", ["hds_gemm", "hds_gemm_2sm", "hds_gemm_fp8", "hds_quantize_fp8_rows", "hds_norm"])
 RaggedOpsBuilder = _mk("ragged_device_ops", "cuda", ["hds_paged_attention_splitkv", "hds_paged_attention_prefill", "hds_embed",
                                                        "hds_rope_kv_append", "hds_gather_rows", "hds_moe_topk_gating",
                                                        "hds_moe_scatter", "hds_moe_gather"])
@@ -68,13 +68,24 @@ SparseAttnBuilder = _mk("sparse_attn", "cuda", [])
 RandomLTDBuilder = _mk("random_ltd", "cuda", [])
 SpatialInferenceBuilder = _mk("spatial_inference", "cuda", [])
 EvoformerAttnBuilder = _mk("evoformer_attn", "cuda", [])
-UtilsBuilder = _mk("utils", "host", [])
+ShareMemCommBuilder = _mk("deepspeed_shm_comm", "host", ["hds_shm_open", "hds_shm_allreduce", "hds_shm_close"])
+
+
+class UtilsBuilder(OpBuilder):
+    """``UtilsBuilder().load()`` exposes ``flatten`` / ``unflatten`` (``csrc/utils/flatten_unflatten.cpp``: thin
+    wrappers over torch's dense-tensor flattening, which is what they are here too)."""
+    NAME, LIB = "utils", "host"
+
+    def load(self, verbose: bool = True):
+        from types import SimpleNamespace
+        from torch._utils import _flatten_dense_tensors, _unflatten_dense_tensors
+        return SimpleNamespace(flatten=_flatten_dense_tensors, unflatten=_unflatten_dense_tensors)
 
 ALL_OPS: Dict[str, OpBuilder] = {b.NAME: b() for b in (
     InferenceCoreBuilder, RaggedOpsBuilder, InferenceCutlassBuilder, RaggedUtilsBuilder, InferenceBuilder, AsyncIOBuilder,
     GDSBuilder, QuantizerBuilder, FPQuantizerBuilder, FusedAdamBuilder, FusedLionBuilder, FusedLambBuilder, CPUAdamBuilder,
     CPUAdagradBuilder, CPULionBuilder, TransformerBuilder, StochasticTransformerBuilder, SparseAttnBuilder, RandomLTDBuilder,
-    SpatialInferenceBuilder, EvoformerAttnBuilder, UtilsBuilder)}
+    SpatialInferenceBuilder, EvoformerAttnBuilder, UtilsBuilder, ShareMemCommBuilder)}
 
 
 def get_builder_class(class_name: str):
