@@ -27,6 +27,9 @@ def parse_args(args=None):
     p.add_argument("--no_local_rank", action="store_true")
     p.add_argument("--save_pid", type=int, default=0)
     p.add_argument("--enable_each_rank_log", default="None", type=str)
+    p.add_argument("--enable_elastic_training", action="store_true",
+                   help="supervise the local ranks with the elastic agent: restart the group on failure")
+    p.add_argument("--max_elastic_restarts", type=int, default=3)
     p.add_argument("training_script", type=str)
     p.add_argument("training_script_args", nargs=argparse.REMAINDER)
     return p.parse_args(args=args)
@@ -81,6 +84,17 @@ def main(args=None):
     log_dir = None if args.enable_each_rank_log == "None" else args.enable_each_rank_log
     if log_dir:
         os.makedirs(log_dir, exist_ok=True)
+    if args.enable_elastic_training:
+        # ref launch.py:190-208: hand the local ranks to the elastic agent (restart on failure, bounded)
+        from ..elasticity.elastic_agent import DSElasticAgent, WorkerState
+        cmd = ([sys.executable, "-u"] + (["-m"] if args.module else []) if not args.no_python else []) + \
+            [args.training_script] + args.training_script_args
+        agent = DSElasticAgent(cmd, len(local_slots), env={k: env[k] for k in ("CROSS_RANK", "CROSS_SIZE", "LOCAL_SIZE",
+                                                                               "CUDA_VISIBLE_DEVICES") if k in env},
+                               max_restarts=args.max_elastic_restarts, master_addr=args.master_addr,
+                               master_port=args.master_port, node_rank=args.node_rank,
+                               membership_fn=lambda: len(node_list), log_dir=log_dir)
+        sys.exit(0 if agent.run().state == WorkerState.SUCCEEDED else 1)
     for local_rank, _slot in enumerate(local_slots):
         rank = global_rank_mapping[local_node][local_rank]
         e = env.copy()

@@ -368,3 +368,37 @@ def test_shim_packages_and_random_ltd_autograd():
         kept.scatter_(1, idx[0].long(), 1.0)
         want = (1 + kept)[:, :, None].expand(3, 12, 4)       # dropped tokens: identity; kept tokens: 2x path
         torch.testing.assert_close(x.grad if batch_first else x.grad.transpose(0, 1), want)
+
+
+def test_elastic_agent_restarts_and_rescales(tmp_path):
+    """A failing worker group is restarted (restart count exported); a membership change relaunches with the new world
+    size without consuming a restart; restarts are bounded (ref: elasticity/elastic_agent.py:127-190)."""
+    import sys
+    from hcache_deepspeed_b200.elasticity.elastic_agent import DSElasticAgent, WorkerState
+    marks = tmp_path / "marks"
+    marks.mkdir()
+    script = tmp_path / "worker.py"
+    script.write_text(
+        "import os, sys, time\n"
+        "a = int(os.environ['TORCHELASTIC_RESTART_COUNT']); r = os.environ['RANK']; w = os.environ['WORLD_SIZE']\n"
+        f"open(os.path.join({str(marks)!r}, f'a{{a}}_r{{r}}_w{{w}}'), 'w').close()\n"
+        "mode = sys.argv[1]\n"
+        "if mode == 'flaky' and a == 0 and r == '1': sys.exit(3)\n"
+        "if mode == 'always': sys.exit(5)\n"
+        "if mode == 'scale' and w == '2': time.sleep(30)\n"
+        "time.sleep(0.2)\n")
+    res = DSElasticAgent([sys.executable, str(script), "flaky"], 2, max_restarts=2, monitor_interval=0.05).run()
+    assert res.state == WorkerState.SUCCEEDED and res.restarts == 1 and res.world_sizes == [2, 2]
+    # (rank 0 of attempt 0 may be stopped before it gets to write its mark)
+    assert {"a0_r1_w2", "a1_r0_w2", "a1_r1_w2"} <= set(os.listdir(marks))
+    res = DSElasticAgent([sys.executable, str(script), "always"], 1, max_restarts=1, monitor_interval=0.05).run()
+    assert res.state == WorkerState.FAILED and res.restarts == 1 and res.return_codes[0] == 5
+    nodes = iter([1, 1, 1, 2])
+    last = [1]
+
+    def members():
+        last[0] = next(nodes, last[0] if last[0] == 2 else 2)
+        return last[0]
+
+    res = DSElasticAgent([sys.executable, str(script), "scale"], 2, max_restarts=0, monitor_interval=0.05, membership_fn=members).run()
+    assert res.state == WorkerState.SUCCEEDED and res.restarts == 0 and res.world_sizes == [2, 4]
