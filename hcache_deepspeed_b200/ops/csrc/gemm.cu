@@ -121,6 +121,8 @@ struct Operands {
 int gemm_2sm_dispatch(const void* A, int64_t lda_bytes, const float* a_scale, const void* W, int64_t ldw_bytes,
                       const float* w_scale, int M, int N, int K, bool fp8, bool bf16, int epilogue, int act, const void* bias,
                       void* out, int64_t ldo, int bn, cudaStream_t stream);
+int gemm_2sm_dispatch_rope(const GemmArgs& g, const void* A, int64_t lda_bytes, const void* W, int64_t ldw_bytes, bool bf16,
+                           bool has_q, cudaStream_t stream);
 static bool pair_enabled() {
     static const int on = getenv("HDS_GEMM_2SM") ? atoi(getenv("HDS_GEMM_2SM")) : 1;
     return on != 0;
@@ -411,7 +413,18 @@ static int gemm_rope_common(bool has_q, const void* A, int64_t lda, const void* 
     const long m_tiles = (M + kGemmBM - 1) / kGemmBM;
     int bn = head_dim;
     if (m_tiles * ((N + 255) / 256) >= sm_count()) bn = 256;
-    int rc = prepare(g, ops, A, lda, W, ldw, M, N, K, dtype == 0, bn, 1);
+    // prefill-size problems with 128-wide heads: the CTA-pair kernel (same epilogue, M = 256 tiles over two SMs)
+    const bool pair = head_dim == 128 && M > 128 && ldw >= 0 && g_peer_maps == nullptr && pair_enabled() &&
+                      lda % 8 == 0 && ldw % 8 == 0 && K % 8 == 0 &&
+                      static_cast<int64_t>((M + 255) / 256) * ((N + 255) / 256) * 2 >= sm_count();
+    int rc = 0;
+    if (pair) {
+        g.M = M;
+        g.N = N;
+        g.K = K;
+    } else {
+        rc = prepare(g, ops, A, lda, W, ldw, M, N, K, dtype == 0, bn, 1);
+    }
     if (rc) return rc;
     g.bias = bias;
     g.q_out = q_out;
@@ -423,6 +436,8 @@ static int gemm_rope_common(bool has_q, const void* A, int64_t lda, const void* 
     g.n_kv_heads = n_kv_heads;
     g.block_size = block_size;
     g.do_rope = do_rope;
+    if (pair)
+        return gemm_2sm_dispatch_rope(g, A, lda * 2, W, ldw * 2, dtype == 0, has_q, static_cast<cudaStream_t>(stream));
     const int grid = grid_for(g, bn);
     cudaStream_t s = static_cast<cudaStream_t>(stream);
     if (has_q)

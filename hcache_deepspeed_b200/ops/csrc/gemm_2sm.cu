@@ -97,7 +97,7 @@ struct Gemm2smArgs {
     const float* w_scale;  // fp8 only: [N]
 };
 
-template <int BN, bool kFp8, bool kBf16, bool kGated>
+template <int BN, bool kFp8, bool kBf16, int EPI>
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kGemmThreads, 1)
 gemm_2sm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_w, const Gemm2smArgs fa) {
     constexpr int STAGES = k2sm_stages(BN);
@@ -106,6 +106,9 @@ gemm_2sm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constan
     constexpr int KB_ELEMS = kFp8 ? 128 : 64;            // elements of K in one 128-byte k-block
     constexpr int MMA_K = kFp8 ? 32 : 16;                // elements of K per instruction (32 bytes either way)
     constexpr uint32_t IDESC = kFp8 ? make_idesc_f8(256, BN) : make_idesc_f16(256, BN, kBf16, false, false);
+    constexpr bool kGated = EPI == EPI_GATED;
+    constexpr bool kRope = EPI == EPI_KV_ROPE || EPI == EPI_QKV_ROPE;  // RoPE + paged-KV epilogue (head_dim 128)
+    static_assert(!(kRope && kFp8), "the RoPE epilogues take 16-bit operands");
     const GemmArgs& args = fa.g;
 
     extern __shared__ uint8_t smem_raw[];
@@ -207,8 +210,9 @@ gemm_2sm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constan
             const int row = m_t * 256 + static_cast<int>(rank) * 128 + quad * 32 + lane;
             float sa = 1.0f;
             if constexpr (kFp8) sa = row < args.M ? fa.a_scale[row] : 0.0f;
+            if constexpr (kRope) epilogue_kv_rope<BN, 128, kBf16, EPI == EPI_QKV_ROPE>(args, taddr, row, n_t);
 #pragma unroll 1
-            for (int c = 0; c < BN; c += 32) {
+            for (int c = 0; c < (kRope ? 0 : BN); c += 32) {
                 uint32_t r[32];
                 tmem_ld_32x32(taddr + c, r);
                 tmem_ld_wait();
@@ -258,9 +262,9 @@ gemm_2sm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constan
     }
 }
 
-template <int BN, bool kFp8, bool kBf16, bool kGated>
+template <int BN, bool kFp8, bool kBf16, int EPI>
 static int launch_2sm_inst(const CUtensorMap& ta, const CUtensorMap& tw, const Gemm2smArgs& fa, int grid, cudaStream_t stream) {
-    auto kern = gemm_2sm_kernel<BN, kFp8, kBf16, kGated>;
+    auto kern = gemm_2sm_kernel<BN, kFp8, kBf16, EPI>;
     static bool configured[64] = {false};
     int dev = 0;
     cudaGetDevice(&dev);
@@ -277,10 +281,10 @@ template <bool kFp8, bool kBf16>
 static int launch_2sm(int bn, bool gated, const CUtensorMap& ta, const CUtensorMap& tw, const Gemm2smArgs& fa, int grid,
                       cudaStream_t s) {
     if (bn == 256)
-        return gated ? launch_2sm_inst<256, kFp8, kBf16, true>(ta, tw, fa, grid, s)
-                     : launch_2sm_inst<256, kFp8, kBf16, false>(ta, tw, fa, grid, s);
-    return gated ? launch_2sm_inst<128, kFp8, kBf16, true>(ta, tw, fa, grid, s)
-                 : launch_2sm_inst<128, kFp8, kBf16, false>(ta, tw, fa, grid, s);
+        return gated ? launch_2sm_inst<256, kFp8, kBf16, EPI_GATED>(ta, tw, fa, grid, s)
+                     : launch_2sm_inst<256, kFp8, kBf16, EPI_STORE>(ta, tw, fa, grid, s);
+    return gated ? launch_2sm_inst<128, kFp8, kBf16, EPI_GATED>(ta, tw, fa, grid, s)
+                 : launch_2sm_inst<128, kFp8, kBf16, EPI_STORE>(ta, tw, fa, grid, s);
 }
 
 // Shared host path: operands are 16-bit (a_scale == nullptr) or E4M3 with row / channel scales.
@@ -326,6 +330,27 @@ int gemm_2sm_dispatch(const void* A, int64_t lda_bytes, const float* a_scale, co
                          : launch_2sm<true, false>(bn, gated, ta, tw, fa, grid, stream);
     return bf16 ? launch_2sm<false, true>(bn, gated, ta, tw, fa, grid, stream)
                 : launch_2sm<false, false>(bn, gated, ta, tw, fa, grid, stream);
+}
+
+// QKV / KV projection with the RoPE + paged-KV epilogue on the pair kernel. `g` carries the epilogue fields
+// (bias, q_out, kv_cache, tok_pos, tok_slot, inv_freq, head counts, block_size, do_rope) and M, N, K; head_dim is 128.
+int gemm_2sm_dispatch_rope(const GemmArgs& g, const void* A, int64_t lda_bytes, const void* W, int64_t ldw_bytes, bool bf16,
+                           bool has_q, cudaStream_t stream) {
+    Gemm2smArgs fa;
+    memset(&fa, 0, sizeof(fa));
+    fa.g = g;
+    CUtensorMap ta, tw;
+    int rc = make_tmap_2d_16b(&ta, A, g.K, g.M, lda_bytes, 64, 128, bf16);
+    if (rc) return rc;
+    rc = make_tmap_2d_16b(&tw, W, g.K, g.N, ldw_bytes, 64, 128, bf16);
+    if (rc) return rc;
+    const int work = ((g.M + 255) / 256) * ((g.N + 255) / 256);
+    const int pairs = work < sm_count() / 2 ? work : sm_count() / 2;
+    if (has_q)
+        return bf16 ? launch_2sm_inst<256, false, true, EPI_QKV_ROPE>(ta, tw, fa, 2 * pairs, stream)
+                    : launch_2sm_inst<256, false, false, EPI_QKV_ROPE>(ta, tw, fa, 2 * pairs, stream);
+    return bf16 ? launch_2sm_inst<256, false, true, EPI_KV_ROPE>(ta, tw, fa, 2 * pairs, stream)
+                : launch_2sm_inst<256, false, false, EPI_KV_ROPE>(ta, tw, fa, 2 * pairs, stream);
 }
 
 }  // namespace hds

@@ -266,7 +266,8 @@ def test_kv_blocks_copy_roundtrip():
 # ------------------------------------------------------------------------------------------------
 @pytest.mark.parametrize("dtype", DTYPES)
 @pytest.mark.parametrize("T,H,n_kv,d,rope", [(200, 512, 4, 128, True), (1000, 1024, 8, 128, True), (70, 768, 12, 64, False),
-                                             (33, 256, 2, 64, True)])
+                                             (33, 256, 2, 64, True), (1100, 512, 32, 128, True),   # last two: CTA-pair kernel
+                                             (700, 256, 40, 128, False)])
 def test_restore_kv_proj(dtype, T, H, n_kv, d, rope):
     torch.manual_seed(10)
     bs = 64 if d == 128 else 128
@@ -288,10 +289,11 @@ def test_restore_kv_proj(dtype, T, H, n_kv, d, rope):
     torch.testing.assert_close(cache.float(), want, **tol(dtype))
 
 
-def test_qkv_rope_proj():
+@pytest.mark.parametrize("T,n_q,n_kv", [(150, 4, 2), (1100, 32, 8)])   # the second shape takes the CTA-pair kernel
+def test_qkv_rope_proj(T, n_q, n_kv):
     torch.manual_seed(11)
-    T, H, n_q, n_kv, d, bs = 150, 512, 4, 2, 128, 64
-    n_blocks = 5
+    H, d, bs = 512, 128, 64
+    n_blocks = (T + bs - 1) // bs + 2
     x = rand(T, H)
     w = rand((n_q + 2 * n_kv) * d, H, scale=H ** -0.5)
     pos = torch.arange(T, device="cuda", dtype=torch.int32)
