@@ -73,3 +73,48 @@ def initialize(*args, **kwargs):
     """Training entry point (``deepspeed.initialize``): see :mod:`hcache_deepspeed_b200.runtime`."""
     from .runtime.engine import initialize as _initialize
     return _initialize(*args, **kwargs)
+
+
+# ---- the rest of the ``deepspeed`` top-level namespace, resolved on first use (keeps ``import`` light) --------------
+_LAZY_MODULES = {
+    "zero": ".runtime.zero", "moe": ".moe", "pipe": ".pipe", "checkpoint": ".checkpoint", "module_inject": ".module_inject",
+    "ops": ".ops", "utils": ".utils", "runtime": ".runtime", "inference": ".inference", "sequence": ".sequence",
+    "compression": ".compression", "autotuning": ".autotuning", "elasticity": ".elasticity", "launcher": ".launcher",
+    "monitor": ".monitor", "profiling": ".profiling", "accelerator": ".accelerator", "linear": ".linear", "nvme": ".nvme",
+    "model_implementations": ".model_implementations", "checkpointing": ".runtime.activation_checkpointing.checkpointing",
+}
+_LAZY_ATTRS = {
+    "DeepSpeedEngine": (".runtime.engine", "DeepSpeedEngine"), "DeepSpeedConfig": (".runtime.config", "DeepSpeedConfig"),
+    "DeepSpeedHybridEngine": (".runtime.hybrid_engine", "DeepSpeedHybridEngine"),
+    "PipelineEngine": (".runtime.pipe.engine", "PipelineEngine"), "PipelineModule": (".runtime.pipe.module", "PipelineModule"),
+    "InferenceEngine": (".inference.engine", "InferenceEngine"),
+    "DeepSpeedInferenceConfig": (".inference.config", "DeepSpeedInferenceConfig"),
+    "DeepSpeedTransformerInference": (".model_implementations", "DeepSpeedTransformerInference"),
+    "DeepSpeedTransformerLayer": (".ops.transformer.transformer", "DeepSpeedTransformerLayer"),
+    "DeepSpeedTransformerConfig": (".ops.transformer.transformer", "DeepSpeedTransformerConfig"),
+    "OnDevice": (".utils.init_on_device", "OnDevice"), "tp_model_init": (".runtime.tensor_parallel.tp_manager", "tp_model_init"),
+    "get_accelerator": (".accelerator", "get_accelerator"),
+}
+
+
+def __getattr__(name: str):
+    import importlib
+    if name in _LAZY_MODULES:
+        mod = importlib.import_module(_LAZY_MODULES[name], __name__)
+        globals()[name] = mod
+        return mod
+    if name in _LAZY_ATTRS:
+        mod_name, attr = _LAZY_ATTRS[name]
+        value = getattr(importlib.import_module(mod_name, __name__), attr)
+        globals()[name] = value
+        return value
+    raise AttributeError(f"module {__name__!r} has no attribute {name!r}")
+
+
+def __dir__():
+    return sorted(set(globals()) | set(_LAZY_MODULES) | set(_LAZY_ATTRS))
+
+
+def is_compile_supported() -> bool:
+    """``torch.compile`` is never the hot path here (kernels are hand-written); DeepCompile is declined (``compile/``)."""
+    return False

@@ -402,3 +402,14 @@ def test_elastic_agent_restarts_and_rescales(tmp_path):
 
     res = DSElasticAgent([sys.executable, str(script), "scale"], 2, max_restarts=0, monitor_interval=0.05, membership_fn=members).run()
     assert res.state == WorkerState.SUCCEEDED and res.restarts == 0 and res.world_sizes == [2, 4]
+
+
+def test_top_level_namespace_mirrors_deepspeed():
+    import hcache_deepspeed_b200 as ds
+    for name in ("zero", "moe", "pipe", "checkpoint", "module_inject", "ops", "checkpointing", "DeepSpeedEngine", "PipelineModule",
+                 "InferenceEngine", "DeepSpeedInferenceConfig", "DeepSpeedTransformerInference", "OnDevice", "tp_model_init",
+                 "init_inference", "initialize", "init_distributed", "add_config_arguments", "comm"):
+        assert getattr(ds, name) is not None, name
+    assert hasattr(ds.zero, "Init") and hasattr(ds.pipe, "PipelineModule") and not ds.is_compile_supported()
+    with pytest.raises(AttributeError):
+        ds.no_such_thing
