@@ -123,6 +123,7 @@ int gemm_2sm_dispatch(const void* A, int64_t lda_bytes, const float* a_scale, co
                       void* out, int64_t ldo, int bn, cudaStream_t stream);
 int gemm_2sm_dispatch_rope(const GemmArgs& g, const void* A, int64_t lda_bytes, const void* W, int64_t ldw_bytes, bool bf16,
                            bool has_q, cudaStream_t stream);
+bool is_local_device_ptr(const void* p);
 static bool pair_enabled() {
     static const int on = getenv("HDS_GEMM_2SM") ? atoi(getenv("HDS_GEMM_2SM")) : 1;
     return on != 0;
@@ -293,7 +294,8 @@ extern "C" int hds_gemm(const void* A, int64_t lda, const void* W, int64_t ldw, 
     // measured (profiles/kernel_bench_gemm_2sm.txt): with at least one full wave of 256 x 256 pair tiles the
     // cta_group::2 kernel is 1.10-1.20x the single-CTA kernel and level with cuBLAS
     if (bn == 0 && M > 128 && ldw >= 0 && pair_enabled() && lda % 8 == 0 && ldw % 8 == 0 && K % 8 == 0 &&
-        static_cast<int64_t>((M + 255) / 256) * ((N + 255) / 256) * 2 >= sm_count())
+        static_cast<int64_t>((M + 255) / 256) * ((N + 255) / 256) * 2 >= sm_count() && is_local_device_ptr(A) &&
+        is_local_device_ptr(W))
         return hds::gemm_2sm_dispatch(A, lda * 2, nullptr, W, ldw * 2, nullptr, M, N, K, false, dtype == 0, epilogue, act, bias, out,
                                  ldo, 256, static_cast<cudaStream_t>(stream));
     GemmArgs g;
@@ -416,7 +418,8 @@ static int gemm_rope_common(bool has_q, const void* A, int64_t lda, const void* 
     // prefill-size problems with 128-wide heads: the CTA-pair kernel (same epilogue, M = 256 tiles over two SMs)
     const bool pair = head_dim == 128 && M > 128 && ldw >= 0 && g_peer_maps == nullptr && pair_enabled() &&
                       lda % 8 == 0 && ldw % 8 == 0 && K % 8 == 0 &&
-                      static_cast<int64_t>((M + 255) / 256) * ((N + 255) / 256) * 2 >= sm_count();
+                      static_cast<int64_t>((M + 255) / 256) * ((N + 255) / 256) * 2 >= sm_count() &&
+                      is_local_device_ptr(A) && is_local_device_ptr(W);
     int rc = 0;
     if (pair) {
         g.M = M;

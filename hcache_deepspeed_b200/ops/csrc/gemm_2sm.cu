@@ -12,6 +12,9 @@
 //   * operand kinds: bf16 / fp16 (`kind::f16`, k-block = 64 elements) and E4M3 (`kind::f8f6f4`, k-block = 128 elements,
 //     per-row / per-channel scales in the epilogue) share the kernel: a stage is 128 bytes of K either way.
 //
+// Operands must live in THIS GPU's memory: every host entry checks the operand pointers (cudaPointerGetAttributes) and
+// refuses anything else, and the peer-sharded restore (hds_restore_kv_proj_peers) stays on the single-CTA kernel.
+//
 // Single-CTA kernels (gemm_core.cuh, gemm_fp8.cu) remain for M <= 128, split-K, grouped and fused-epilogue variants.
 // Reference role: the cuBLAS / CUTLASS GEMMs behind `blas_kernels` and `cutlass_ops` (inference/v2/kernels).
 #include <stdlib.h>
@@ -287,6 +290,18 @@ static int launch_2sm(int bn, bool gated, const CUtensorMap& ta, const CUtensorM
                  : launch_2sm_inst<128, kFp8, kBf16, EPI_STORE>(ta, tw, fa, grid, s);
 }
 
+// true iff `p` is ordinary device memory owned by the current GPU (not a peer mapping, not host / managed memory)
+bool is_local_device_ptr(const void* p) {
+    cudaPointerAttributes at;
+    if (cudaPointerGetAttributes(&at, p) != cudaSuccess) {
+        cudaGetLastError();
+        return false;
+    }
+    int dev = -1;
+    cudaGetDevice(&dev);
+    return at.type == cudaMemoryTypeDevice && at.device == dev;
+}
+
 // Shared host path: operands are 16-bit (a_scale == nullptr) or E4M3 with row / channel scales.
 int gemm_2sm_dispatch(const void* A, int64_t lda_bytes, const float* a_scale, const void* W, int64_t ldw_bytes,
                       const float* w_scale, int M, int N, int K, bool fp8, bool bf16, int epilogue, int act, const void* bias,
@@ -298,6 +313,10 @@ int gemm_2sm_dispatch(const void* A, int64_t lda_bytes, const float* a_scale, co
     if (bn != 128 && bn != 256) {
         set_error("CTA-pair GEMM: bn must be 128 or 256");
         return HDS_ERR_BAD_ARG;
+    }
+    if (!is_local_device_ptr(A) || !is_local_device_ptr(W)) {
+        set_error("CTA-pair GEMM: operands must be this GPU's own device memory");
+        return HDS_ERR_UNSUPPORTED;
     }
     Gemm2smArgs fa;
     memset(&fa, 0, sizeof(fa));
@@ -336,6 +355,10 @@ int gemm_2sm_dispatch(const void* A, int64_t lda_bytes, const float* a_scale, co
 // (bias, q_out, kv_cache, tok_pos, tok_slot, inv_freq, head counts, block_size, do_rope) and M, N, K; head_dim is 128.
 int gemm_2sm_dispatch_rope(const GemmArgs& g, const void* A, int64_t lda_bytes, const void* W, int64_t ldw_bytes, bool bf16,
                            bool has_q, cudaStream_t stream) {
+    if (!is_local_device_ptr(A) || !is_local_device_ptr(W)) {
+        set_error("CTA-pair GEMM: operands must be this GPU's own device memory");
+        return HDS_ERR_UNSUPPORTED;
+    }
     Gemm2smArgs fa;
     memset(&fa, 0, sizeof(fa));
     fa.g = g;
