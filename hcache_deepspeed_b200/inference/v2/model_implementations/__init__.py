@@ -90,9 +90,16 @@ class InferenceV2Policy:
         if tp_size > 1 and device.type == "cuda" and engine_config.tensor_parallel.fused_collectives:
             from ....parallel.tp_comm import make_tp_comm
             comm = make_tp_comm(mp_group, tp_size, tp_rank, device)
-        return RaggedTransformer(self.arch, weights, engine_config.state_manager, dtype=dtype, device=device,
-                                 tp_rank=tp_rank, tp_size=tp_size, comm=comm,
-                                 capture_latents=engine_config.hcache.enabled)
+        model = RaggedTransformer(self.arch, weights, engine_config.state_manager, dtype=dtype, device=device,
+                                  tp_rank=tp_rank, tp_size=tp_size, comm=comm,
+                                  capture_latents=engine_config.hcache.enabled)
+        mode = getattr(getattr(engine_config, "quantization", None), "quantization_mode", None)
+        if mode == "wf8af8":
+            model.quantize_weights_fp8()
+        elif mode is not None:
+            raise ValueError(f"quantization_mode {mode!r} is not available: use 'wf8af8' (the reference's 'wf6af16' kernel is "
+                             "sm_80-only; see DESIGN.md)")
+        return model
 
 
 # names of the reference's per-family policies (all share the one implementation above)

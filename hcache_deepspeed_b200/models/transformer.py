@@ -27,6 +27,7 @@ from ..inference.v2.ragged import DSStateManager, KVCacheConfig, RaggedBatchWrap
 from ..inference.v2.ragged.manager_configs import DSStateManagerConfig
 from ..ops import reference as ref
 from ..ops.backend import MAX_DECODE_SPLITS, get_ops, pick_decode_splits
+from ..ops.fp8 import Fp8Weight
 from ..ops.kernels import ACT_CODES
 from .arch import ArchSpec
 from .weights import ModelWeights, shard_info
@@ -254,6 +255,31 @@ class RaggedTransformer:
         return
 
     # ------------------------------------------------------------------------------------------------
+    # W8A8 (fp8) weights
+    # ------------------------------------------------------------------------------------------------
+    def quantize_weights_fp8(self) -> int:
+        """``quantization_mode = "wf8af8"``: convert every layer's QKV / attention-out / MLP weights to E4M3 with
+        per-output-channel scales (embedding, LM head and norms stay 16-bit). Returns the bytes saved."""
+        s = self.spec
+        if self.tp_size > 1 or s.is_moe or s.parallel_residual:
+            raise NotImplementedError("wf8af8 covers dense, sequential-residual models on one GPU (tensor-parallel, "
+                                      "mixture-of-experts and parallel-residual blocks reduce through fp32 partial sums)")
+        saved = 0
+        for lw in self.w.layers:
+            for name in ("w_qkv", "w_o", "w_up", "w_down"):
+                w = getattr(lw, name)
+                if isinstance(w, torch.Tensor):
+                    q = Fp8Weight.from_tensor(w)
+                    saved += w.numel() * w.element_size() - q.nbytes()
+                    setattr(lw, name, q)
+        ks = set()
+        for lw in self.w.layers:
+            ks |= {int(lw.w_qkv.shape[1]), int(lw.w_o.shape[1]), int(lw.w_up.shape[1]), int(lw.w_down.shape[1])}
+        self.ops.reserve_fp8(self._state_config.max_ragged_batch_size, sorted(ks), self.device)
+        self.fp8 = True
+        return saved
+
+    # ------------------------------------------------------------------------------------------------
     # forward
     # ------------------------------------------------------------------------------------------------
     def _norm(self, x, gamma, out, beta=None, delta=None, res_out=None) -> torch.Tensor:
@@ -274,6 +300,8 @@ class RaggedTransformer:
     def _row_parallel(self, x: torch.Tensor, w: torch.Tensor, b: Optional[torch.Tensor], T: int, force_accum: bool,
                       last_into_delta: bool = True) -> torch.Tensor:
         """y = x @ w.T (+b), left as the pending delta. fp32 partial sums when the GEMM is split over K or ranks."""
+        if isinstance(w, Fp8Weight):
+            return self.ops.gemm(x, w, self.delta16[:T], bias=b)   # W8A8: scaled store epilogue, 16-bit pending delta
         if force_accum or T <= ACCUM_MAX_TOKENS or self.tp_size > 1:
             d32 = self._delta_bufs[self._delta_idx][:T]
             self.ops.gemm_accum(x, w, d32, bias=b, comm=self.comm)

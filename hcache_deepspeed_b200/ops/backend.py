@@ -15,6 +15,15 @@ from typing import Optional
 import torch
 
 from . import reference as ref
+from .fp8 import Fp8Weight, quantize_rows_reference
+
+
+def _fp8_emulate(a, w):
+    """CPU restatement of the W8A8 path: fp8-round the activations per token, de-quantise both operands to fp32."""
+    if not isinstance(w, Fp8Weight):
+        return a, w
+    q, s = quantize_rows_reference(a)
+    return q.view(torch.float8_e4m3fn).float() * s[:, None], w.dequantize()
 
 
 class CpuOps:
@@ -22,11 +31,16 @@ class CpuOps:
 
     # ---- linear ---------------------------------------------------------------------------------
     def gemm(self, a, w, out, bias=None, act=0, gated=False, workspace=None):
-        out.copy_(ref.gemm(a, w, bias=bias, act=act, gated=gated))
+        a, w = _fp8_emulate(a, w)
+        out.copy_(ref.gemm(a, w, bias=bias, act=act, gated=gated, out_dtype=out.dtype))
         return out
 
     def gemm_accum(self, a, w, accum, bias=None, comm=None):
+        a, w = _fp8_emulate(a, w)
         accum += ref.gemm(a, w, bias=bias, out_dtype=torch.float32)
+
+    def reserve_fp8(self, max_tokens, ks, device) -> None:
+        pass
 
     # ---- norm -----------------------------------------------------------------------------------
     def norm(self, x, gamma, out, beta=None, delta=None, zero_delta=False, res_out=None, eps=1e-5, layer_norm=False,
@@ -45,7 +59,9 @@ class CpuOps:
     def qkv_rope_kv_append(self, x, w_qkv, b_qkv, qkv_buf, q_out, kv_layer, tok_pos, tok_slot, inv_freq, n_q, n_kv, d,
                            rot_dim, block_size, workspace=None):
         T = x.shape[0]
-        qkv = ref.gemm(x, w_qkv, bias=b_qkv)
+        dt = x.dtype
+        x, w_qkv = _fp8_emulate(x, w_qkv)
+        qkv = ref.gemm(x, w_qkv, bias=b_qkv, out_dtype=dt)
         q, k, v = qkv.split([n_q * d, n_kv * d, n_kv * d], dim=1)
         q, k, v = q.reshape(T, n_q, d), k.reshape(T, n_kv, d), v.reshape(T, n_kv, d)
         if inv_freq is not None:
@@ -57,7 +73,9 @@ class CpuOps:
     def restore_kv_proj(self, latents, w_kv, b_kv, kv_layer, tok_pos, tok_slot, inv_freq, n_kv, d, rot_dim, block_size,
                         scratch=None):
         T = latents.shape[0]
-        kv = ref.gemm(latents, w_kv, bias=b_kv)
+        dt = latents.dtype
+        latents, w_kv = _fp8_emulate(latents, w_kv)
+        kv = ref.gemm(latents, w_kv, bias=b_kv, out_dtype=dt)
         k, v = kv[:, :n_kv * d].reshape(T, n_kv, d), kv[:, n_kv * d:].reshape(T, n_kv, d)
         if inv_freq is not None:
             k = ref.rope_rotate_half(k, tok_pos, inv_freq, rot_dim)
@@ -94,11 +112,35 @@ class CudaOps:
         from . import kernels
         self.k = kernels
 
+    def _fp8_act(self, a):
+        """Per-token E4M3 quantisation of ``a`` into persistent buffers (no allocation in steady state)."""
+        T, K = a.shape
+        bufs = self.__dict__.setdefault("_fp8_bufs", {})
+        q, s = bufs.get(K, (None, None))
+        if q is None or q.shape[0] < T or q.device != a.device:
+            cap = max(T, 0 if q is None else 2 * q.shape[0], 64)
+            q = torch.empty(cap, K, dtype=torch.uint8, device=a.device)
+            s = torch.empty(cap, dtype=torch.float32, device=a.device)
+            bufs[K] = (q, s)
+        return self.k.quantize_fp8_rows(a, q[:T], s[:T])
+
+    def reserve_fp8(self, max_tokens: int, ks, device) -> None:
+        """Size the activation-quantisation buffers up front (before any CUDA-graph capture)."""
+        bufs = self.__dict__.setdefault("_fp8_bufs", {})
+        for K in ks:
+            bufs[K] = (torch.empty(max_tokens, K, dtype=torch.uint8, device=device),
+                       torch.empty(max_tokens, dtype=torch.float32, device=device))
+
     def gemm(self, a, w, out, bias=None, act=0, gated=False, workspace=None):
+        if isinstance(w, Fp8Weight):
+            aq, a_s = self._fp8_act(a)
+            return self.k.gemm_fp8(aq, a_s, w.q, w.scale, out, bias=bias, act=act, gated=gated)
         return self.k.gemm(a, w, bias=bias, act=act, gated=gated, out=out,
                            workspace=workspace if a.shape[0] <= 128 else None)
 
     def gemm_accum(self, a, w, accum, bias=None, comm=None):
+        if isinstance(w, Fp8Weight):
+            raise NotImplementedError("fp8 weights: the executor routes reducing GEMMs through the 16-bit delta")
         if comm is not None and comm.fused and comm.mode == "push":
             # GEMM -> all-reduce in the epilogue: reduce the tile into every rank's buffer (NVLS multicast / P2P red)
             self.k.gemm_accum(a, w, accum, bias=bias, peer_ptrs=comm.peer_ptrs(accum), multicast_ptr=comm.multicast_ptr(accum))
@@ -118,7 +160,10 @@ class CudaOps:
                            rot_dim, block_size, workspace=None):
         T = x.shape[0]
         fusable = d in (64, 128) and (inv_freq is None or rot_dim == d)
-        if fusable and T >= self.FUSED_QKV_MIN_TOKENS:
+        if isinstance(w_qkv, Fp8Weight):
+            self.gemm(x, w_qkv, qkv_buf, bias=b_qkv)
+            self.k.rope_kv_append(qkv_buf, q_out, kv_layer, tok_pos, tok_slot, inv_freq, n_q, n_kv, d, rot_dim, block_size)
+        elif fusable and T >= self.FUSED_QKV_MIN_TOKENS:
             self.k.qkv_rope_proj(x, w_qkv, q_out, kv_layer, tok_pos, tok_slot, inv_freq, n_q, n_kv, d, block_size,
                                  bias_qkv=b_qkv)
         else:
@@ -127,7 +172,13 @@ class CudaOps:
 
     def restore_kv_proj(self, latents, w_kv, b_kv, kv_layer, tok_pos, tok_slot, inv_freq, n_kv, d, rot_dim, block_size,
                         scratch=None):
-        if d in (64, 128) and (inv_freq is None or rot_dim == d):
+        if isinstance(w_kv, Fp8Weight):
+            if scratch is None or scratch.shape[0] < latents.shape[0]:
+                scratch = torch.empty(latents.shape[0], w_kv.shape[0], dtype=latents.dtype, device=latents.device)
+            scratch = scratch[:latents.shape[0]]
+            self.gemm(latents, w_kv, scratch, bias=b_kv)
+            self.k.rope_kv_append(scratch, scratch, kv_layer, tok_pos, tok_slot, inv_freq, 0, n_kv, d, rot_dim, block_size)
+        elif d in (64, 128) and (inv_freq is None or rot_dim == d):
             self.k.restore_kv_proj(latents, w_kv, kv_layer, tok_pos, tok_slot, inv_freq, n_kv, d, block_size, bias_kv=b_kv)
         else:
             # head sizes the fused epilogue does not cover: plain GEMM into scratch, then RoPE/append with zero

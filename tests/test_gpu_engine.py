@@ -158,3 +158,34 @@ def test_graphed_callable_replays_and_tracks_inputs():
                    torch.randn(1, 7, 8, device="cuda", dtype=torch.half))
         torch.testing.assert_close(u(s, t, e), u.unet(s, t, e), rtol=1e-2, atol=1e-2)
     assert u.cuda_graph_created
+
+
+def test_fp8_engine_mode_gpu():
+    """wf8af8 on the GPU: fp8 tensor-core GEMMs for every layer linear; logits track the bf16 engine, HCache restore
+    reproduces the live KV, and small decode batches (the CUDA-graph path) run with the fp8 kernels inside."""
+    from hcache_deepspeed_b200.inference.v2 import RaggedInferenceEngineConfig, build_engine_from_arch
+    from hcache_deepspeed_b200.models.arch import named_arch
+    spec = named_arch("llama-2-7b").scaled(n_layers=2)
+
+    def build(mode):
+        cfg = RaggedInferenceEngineConfig(state_manager={
+            "max_tracked_sequences": 16, "max_ragged_batch_size": 512, "max_ragged_sequence_count": 8, "max_context": 1024,
+            "memory_config": {"mode": "allocate", "size": 512 * 1024 * 1024}}, hcache={"enabled": True},
+            quantization={"quantization_mode": mode})
+        return build_engine_from_arch(spec, cfg, seed=3, dtype=torch.bfloat16, device=torch.device("cuda"))
+
+    ref_eng, eng = build(None), build("wf8af8")
+    g = torch.Generator().manual_seed(0)
+    prompt = torch.randint(0, spec.vocab, (300, ), generator=g)
+    want, _ = ref_eng.put([1], [prompt])
+    got, lat = eng.put([1], [prompt])
+    cos = torch.nn.functional.cosine_similarity(got.float().flatten(), want.float().flatten(), dim=0)
+    assert cos > 0.98, float(cos)
+    eng.restore_kv([2], [prompt], [lat[0]])
+    nxt = torch.tensor([11])
+    a, _ = eng.put([1], [nxt], capture_latents=False)
+    b, _ = eng.put([2], [nxt], capture_latents=False)
+    torch.testing.assert_close(a.float(), b.float(), rtol=2e-2, atol=6e-2)
+    for _ in range(3):
+        a, _ = eng.put([1, 2], [nxt, nxt], capture_latents=False)
+    assert torch.isfinite(a.float()).all()

@@ -155,3 +155,35 @@ def test_session_manager_multi_turn(tmp_path):
         assert not mgr.is_resident(7) and eng.state_manager.get_sequence(7) is None
         assert st.n_tokens == len(history) and st.hidden.shape[1] == len(history)
     assert store.stats["saves"] == 3 and store.stats["dram_hits"] == 2
+
+
+def test_fp8_engine_mode_cpu():
+    """quantization_mode='wf8af8': layer weights become E4M3 + per-channel scales; logits track the 16/32-bit engine,
+    restore == live KV still holds (both paths project K/V through the same fp8 weights)."""
+    from hcache_deepspeed_b200.ops.fp8 import Fp8Weight
+
+    def build(mode):
+        cfg = RaggedInferenceEngineConfig(state_manager=dict(max_tracked_sequences=16, max_ragged_batch_size=256,
+                                                             max_ragged_sequence_count=8, max_context=512,
+                                                             memory_config=dict(mode="allocate", size=32 * 1024 * 1024)),
+                                          hcache={"enabled": True}, quantization={"quantization_mode": mode})
+        return build_engine_from_arch("tiny-llama-test", cfg, seed=1, dtype=torch.float32, device=torch.device("cpu"))
+
+    ref_eng, eng = build(None), build("wf8af8")
+    lw = eng.model().w.layers[0]
+    assert isinstance(lw.w_qkv, Fp8Weight) and isinstance(lw.w_down, Fp8Weight) and not isinstance(eng.model().w.lm_head, Fp8Weight)
+    torch.testing.assert_close(lw.w_qkv.dequantize(), ref_eng.model().w.layers[0].w_qkv.float(), rtol=0.07, atol=1e-3)
+    g = torch.Generator().manual_seed(0)
+    prompt = torch.randint(0, 100, (40, ), generator=g)
+    want, _ = ref_eng.put([1], [prompt])
+    got, lat = eng.put([1], [prompt])
+    cos = torch.nn.functional.cosine_similarity(got.float().flatten(), want.float().flatten(), dim=0)
+    assert cos > 0.99, float(cos)
+    # restore a second session from the captured hidden states: next-token logits equal the live session's
+    eng.restore_kv([2], [prompt], [lat[0]])
+    nxt = torch.tensor([7])
+    a, _ = eng.put([1], [nxt])
+    b, _ = eng.put([2], [nxt])
+    torch.testing.assert_close(a, b, rtol=1e-4, atol=1e-4)
+    with pytest.raises(ValueError, match="wf8af8"):
+        build("wf6af16")
