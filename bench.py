@@ -42,6 +42,9 @@ def parse():
                    help="N > 1: 'dp' = one full replica per GPU serving its own sessions (a 7B model fits 13x in 180 GB; "
                         "what a deployment does for throughput), 'tp' = one engine tensor-parallel over all GPUs (fused "
                         "NVLink collectives, PCIe-sharded restore: lower TTFT, lower aggregate throughput)")
+    p.add_argument("--quant", default="none", choices=["none", "wf8af8"],
+                   help="none (default, the bf16 headline configuration) or wf8af8: E4M3 weights + per-token fp8 activations; "
+                        "reported with dtype fp8-w8a8 and NOT comparable with the bf16 baseline")
     p.add_argument("--plan", default="hidden", choices=["auto", "hidden"],
                    help="hidden: every layer from hidden states (fastest measured on 1xB200: 20.4 ms vs 21.6 ms); auto: planner mix with a recomputed prefix")
     return p.parse_args()
@@ -116,7 +119,8 @@ def run_ours(a):
                        "max_ragged_sequence_count": max(B, 8), "max_context": max_ctx,
                        "memory_config": {"mode": "allocate",
                                          "size": int((B + 1) * (max_ctx + 128) * spec.kv_bytes_per_token_layer() * spec.n_layers / tp)}},
-        hcache={"enabled": True, "capture": "off", "shard_capture": tp > 1})
+        hcache={"enabled": True, "capture": "off", "shard_capture": tp > 1},
+        quantization={"quantization_mode": None if a.quant == "none" else a.quant})
     eng = build_engine_from_arch(spec, cfg, seed=1234, dtype=torch.bfloat16, device=dev)
     model = eng.model()
     assert native.cuda_lib_loaded(), "sm_100a kernel library was not loaded"
@@ -233,7 +237,7 @@ def run_ours(a):
             "metric": "decode tokens/sec over restored multi-turn sessions (p50 restored-context TTFT in ttft_p50_ms)",
             "value": round(value, 2), "unit": "tokens/s", "n_gpus": world, "steps": a.steps, "warmup": a.warmup,
             "ms_per_step": round(total_ms / a.steps, 3), "higher_is_better": True, "scaling": "weak",
-            "vs_baseline": (value / ref_val) if ref_val else None, "dtype": "bf16",
+            "vs_baseline": (value / ref_val) if ref_val else None, "dtype": "bf16" if a.quant == "none" else "fp8-w8a8",
             "data": "synthetic tokens and hidden states, random-init weights", "impl": "ours",
             "ttft_p50_ms": round(ttft_dev, 3),
             "config": {"model": a.model, "global_batch": B * replicas, "seq_len": ctx + n_new + D,

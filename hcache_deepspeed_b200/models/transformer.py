@@ -34,6 +34,7 @@ from .weights import ModelWeights, shard_info
 
 #: row-parallel GEMMs switch from fp32 partial-sum accumulation (split-K) to plain 16-bit stores above this
 ACCUM_MAX_TOKENS = 256
+FP8_ACCUM_MAX_TOKENS = 64   # fp8 weights: the fp32-accumulate epilogue exists on the decode (feature-major) kernel only
 #: staging slots of the restore pipeline (H2D of layer l+1.. overlaps the projection of layer l)
 RESTORE_SLOTS = 4
 
@@ -300,8 +301,8 @@ class RaggedTransformer:
     def _row_parallel(self, x: torch.Tensor, w: torch.Tensor, b: Optional[torch.Tensor], T: int, force_accum: bool,
                       last_into_delta: bool = True) -> torch.Tensor:
         """y = x @ w.T (+b), left as the pending delta. fp32 partial sums when the GEMM is split over K or ranks."""
-        if isinstance(w, Fp8Weight):
-            return self.ops.gemm(x, w, self.delta16[:T], bias=b)   # W8A8: scaled store epilogue, 16-bit pending delta
+        if isinstance(w, Fp8Weight) and T > FP8_ACCUM_MAX_TOKENS:
+            return self.ops.gemm(x, w, self.delta16[:T], bias=b)   # W8A8 prefill: scaled store epilogue, 16-bit delta
         if force_accum or T <= ACCUM_MAX_TOKENS or self.tp_size > 1:
             d32 = self._delta_bufs[self._delta_idx][:T]
             self.ops.gemm_accum(x, w, d32, bias=b, comm=self.comm)

@@ -134,13 +134,19 @@ class CudaOps:
     def gemm(self, a, w, out, bias=None, act=0, gated=False, workspace=None):
         if isinstance(w, Fp8Weight):
             aq, a_s = self._fp8_act(a)
-            return self.k.gemm_fp8(aq, a_s, w.q, w.scale, out, bias=bias, act=act, gated=gated)
+            return self.k.gemm_fp8(aq, a_s, w.q, w.scale, out, bias=bias, act=act, gated=gated,
+                                   workspace=workspace if a.shape[0] <= 64 else None)
         return self.k.gemm(a, w, bias=bias, act=act, gated=gated, out=out,
                            workspace=workspace if a.shape[0] <= 128 else None)
 
     def gemm_accum(self, a, w, accum, bias=None, comm=None):
         if isinstance(w, Fp8Weight):
-            raise NotImplementedError("fp8 weights: the executor routes reducing GEMMs through the 16-bit delta")
+            if a.shape[0] > 64 or (comm is not None and getattr(comm, "size", 1) > 1):
+                raise NotImplementedError("fp8 weights: above 64 tokens the executor routes reducing GEMMs through the "
+                                          "16-bit delta; tensor-parallel reductions are not covered")
+            aq, a_s = self._fp8_act(a)
+            self.k.gemm_fp8_accum(aq, a_s, w.q, w.scale, accum, bias=bias, out_dtype=a.dtype)
+            return
         if comm is not None and comm.fused and comm.mode == "push":
             # GEMM -> all-reduce in the epilogue: reduce the tile into every rank's buffer (NVLS multicast / P2P red)
             self.k.gemm_accum(a, w, accum, bias=bias, peer_ptrs=comm.peer_ptrs(accum), multicast_ptr=comm.multicast_ptr(accum))

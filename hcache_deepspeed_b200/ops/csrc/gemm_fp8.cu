@@ -11,6 +11,7 @@
 #include <cuda_fp8.h>
 #include <stdlib.h>
 #include "gemm_core.cuh"
+#include "gemm_skinny.cuh"
 #include "hds_host.cuh"
 #include "../../../include/hds_b200.h"
 
@@ -286,4 +287,98 @@ extern "C" int hds_gemm_fp8(const void* Aq, int64_t lda, const float* a_scale, c
                                      : launch_fp8_bn<true, true>(bn, ta, tw, fa, grid, s);
     return epilogue == EPI_STORE ? launch_fp8_bn<false, false>(bn, ta, tw, fa, grid, s)
                                  : launch_fp8_bn<false, true>(bn, ta, tw, fa, grid, s);
+}
+
+// ---- decode-size M: the feature-major weight-streaming kernel (gemm_skinny.cuh) with E4M3 operands --------------
+namespace hds {
+
+template <int NT, int EPI, bool kBf16>
+static int launch_skinny_fp8_inst(const CUtensorMap& tw, const CUtensorMap& tx, const SkinnyArgs& a, int grid, cudaStream_t stream) {
+    auto kern = gemm_skinny_kernel<NT, EPI, kBf16, true>;
+    static bool configured[64] = {false};
+    int dev = 0;
+    cudaGetDevice(&dev);
+    if (!configured[dev & 63]) {
+        HDS_CHECK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                            static_cast<int>(skinny_smem_bytes(NT))));
+        configured[dev & 63] = true;
+    }
+    HDS_CHECK_CUDA(launch_kernel(kern, dim3(grid), dim3(kGemmThreads), skinny_smem_bytes(NT), stream, tw, tx, a));
+    return HDS_OK;
+}
+
+template <int EPI, bool kBf16>
+static int launch_skinny_fp8_nt(int nt, const CUtensorMap& tw, const CUtensorMap& tx, const SkinnyArgs& a, int grid,
+                                cudaStream_t s) {
+    if (nt == 16) return launch_skinny_fp8_inst<16, EPI, kBf16>(tw, tx, a, grid, s);
+    if (nt == 32) return launch_skinny_fp8_inst<32, EPI, kBf16>(tw, tx, a, grid, s);
+    return launch_skinny_fp8_inst<64, EPI, kBf16>(tw, tx, a, grid, s);
+}
+
+}  // namespace hds
+
+extern "C" int64_t hds_gemm_fp8_skinny_workspace_bytes(int M, int N) {
+    const int nt = M <= 16 ? 16 : M <= 32 ? 32 : 64;
+    const int64_t n_tiles = (N + hds::kSkinnyBF - 1) / hds::kSkinnyBF;
+    return ((n_tiles * hds::kSkinnyBF * nt * 4 + 255) & ~int64_t(255)) + n_tiles * 16;
+}
+
+extern "C" int hds_gemm_fp8_skinny(const void* Aq, int64_t lda, const float* a_scale, const void* Wq, int64_t ldw,
+                                   const float* w_scale, int M, int N, int K, int out_dtype, int epilogue, int act,
+                                   const void* bias, void* out, int64_t ldo, float* accum, int64_t ld_accum, void* ws,
+                                   int64_t ws_bytes, int want_splits, void* stream) {
+    using namespace hds;
+    HDS_REQUIRE(epilogue == EPI_STORE || epilogue == EPI_GATED || epilogue == EPI_RED_F32,
+                "hds_gemm_fp8_skinny: epilogue must be 0 (store), 1 (gated) or 2 (fp32 accumulate)");
+    HDS_REQUIRE(out_dtype == 0 || out_dtype == 1, "hds_gemm_fp8_skinny: out dtype must be 0 (bf16) or 1 (fp16)");
+    HDS_REQUIRE(M > 0 && M <= 64 && N > 0 && K > 0 && K % 16 == 0, "hds_gemm_fp8_skinny: 1 <= M <= 64, K a multiple of 16");
+    HDS_REQUIRE(epilogue != EPI_GATED || N % 2 == 0, "hds_gemm_fp8_skinny: gated epilogue needs an even N");
+    HDS_REQUIRE(epilogue != EPI_RED_F32 || accum != nullptr, "hds_gemm_fp8_skinny: accum required");
+    const int nt = M <= 16 ? 16 : M <= 32 ? 32 : 64;
+    const int n_tiles = (N + kSkinnyBF - 1) / kSkinnyBF;
+    const int kb_total = (K + 127) / 128;
+    const int64_t ws_data = (static_cast<int64_t>(n_tiles) * kSkinnyBF * nt * 4 + 255) & ~int64_t(255);
+    const bool can_split = epilogue == EPI_RED_F32 || (ws != nullptr && ws_bytes >= ws_data + static_cast<int64_t>(n_tiles) * 16);
+    int splits = 1;
+    if (can_split) {
+        if (want_splits > 0) {
+            splits = want_splits;
+        } else {
+            splits = sm_count() * skinny_occupancy(nt) / n_tiles;
+            if (splits > kb_total / 4) splits = kb_total / 4;
+            if (splits > 8) splits = 8;
+        }
+        if (splits < 1) splits = 1;
+        if (splits > kb_total) splits = kb_total;
+    }
+    const int per = (kb_total + splits - 1) / splits;
+    splits = (kb_total + per - 1) / per;
+    SkinnyArgs a;
+    memset(&a, 0, sizeof(a));
+    a.M = M; a.N = N; a.K = K;
+    a.splits = splits;
+    a.kb_per_split = per;
+    a.act = act;
+    a.out = out; a.ldo = ldo; a.bias = bias;
+    a.accum = accum; a.ld_accum = ld_accum;
+    a.a_scale = a_scale; a.w_scale = w_scale;
+    if (splits > 1 && epilogue != EPI_RED_F32) {
+        a.ws = reinterpret_cast<float*>(ws);
+        a.tickets = reinterpret_cast<int32_t*>(reinterpret_cast<char*>(ws) + ws_data);
+    }
+    CUtensorMap tw, tx;
+    int rc = make_tmap_2d_8b(&tw, Wq, K, N, ldw, 128, kSkinnyBF);
+    if (rc) return rc;
+    rc = make_tmap_2d_8b(&tx, Aq, K, M, lda, 128, nt);
+    if (rc) return rc;
+    const int grid = n_tiles * splits;
+    cudaStream_t s = static_cast<cudaStream_t>(stream);
+    if (out_dtype == 0) {
+        if (epilogue == EPI_STORE) return launch_skinny_fp8_nt<EPI_STORE, true>(nt, tw, tx, a, grid, s);
+        if (epilogue == EPI_GATED) return launch_skinny_fp8_nt<EPI_GATED, true>(nt, tw, tx, a, grid, s);
+        return launch_skinny_fp8_nt<EPI_RED_F32, true>(nt, tw, tx, a, grid, s);
+    }
+    if (epilogue == EPI_STORE) return launch_skinny_fp8_nt<EPI_STORE, false>(nt, tw, tx, a, grid, s);
+    if (epilogue == EPI_GATED) return launch_skinny_fp8_nt<EPI_GATED, false>(nt, tw, tx, a, grid, s);
+    return launch_skinny_fp8_nt<EPI_RED_F32, false>(nt, tw, tx, a, grid, s);
 }

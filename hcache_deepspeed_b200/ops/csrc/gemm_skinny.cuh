@@ -41,6 +41,8 @@ struct SkinnyArgs {
     int64_t ld_accum;
     float* ws;          // split-K scratch [N][NT] fp32 (store / gated), zero between calls
     int32_t* tickets;   // [n_tiles * 4], zero between calls
+    const float* a_scale;  // fp8 operands only: per-token scales [M]
+    const float* w_scale;  // fp8 operands only: per-feature scales [N]
 };
 
 template <int NT>
@@ -90,7 +92,10 @@ __device__ __forceinline__ void skinny_finalize(const SkinnyArgs& a, int n, uint
     }
 }
 
-template <int NT, int EPI, bool kBf16>
+// kFp8: both operands are E4M3 codes (a 128-byte row of a tile then holds 128 K-elements instead of 64, i.e. half the
+// weight bytes per MAC); the accumulator is scaled by w_scale[feature] * a_scale[token] right after it leaves TMEM, so
+// split-K partial sums and all three epilogues see real-valued numbers. kBf16 then names the OUTPUT / bias dtype.
+template <int NT, int EPI, bool kBf16, bool kFp8 = false>
 __global__ void __launch_bounds__(kGemmThreads, skinny_occupancy(NT))
 gemm_skinny_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_constant__ CUtensorMap tmap_x,
                    const SkinnyArgs args) {
@@ -98,7 +103,8 @@ gemm_skinny_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_cons
     constexpr uint32_t W_BYTES = kSkinnyBF * kGemmBK * 2;
     constexpr uint32_t X_BYTES = NT * kGemmBK * 2;
     constexpr uint32_t TMEM_COLS = NT < 32 ? 32 : NT;
-    constexpr uint32_t IDESC = make_idesc_f16(kSkinnyBF, NT, kBf16, false, false);
+    constexpr uint32_t IDESC = kFp8 ? make_idesc_f8(kSkinnyBF, NT) : make_idesc_f16(kSkinnyBF, NT, kBf16, false, false);
+    constexpr int KB = kFp8 ? 2 * kGemmBK : kGemmBK;  // K-elements per 128-byte tile row
     static_assert(NT == 16 || NT == 32 || NT == 64, "token tile must be 16, 32 or 64");
 
     extern __shared__ uint8_t smem_raw[];
@@ -113,7 +119,7 @@ gemm_skinny_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_cons
     const uint32_t warp = warp_id();
     const uint32_t lane = lane_id();
     const int n_tiles = (args.N + kSkinnyBF - 1) / kSkinnyBF;
-    const int kb_total = (args.K + kGemmBK - 1) / kGemmBK;
+    const int kb_total = (args.K + KB - 1) / KB;
     const int n_t = static_cast<int>(blockIdx.x) % n_tiles;
     const int sp = static_cast<int>(blockIdx.x) / n_tiles;
     const int kb0 = sp * args.kb_per_split;
@@ -147,18 +153,18 @@ gemm_skinny_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_cons
             const int pre = min(STAGES, kb1 - kb0);
             for (int i = 0; i < pre; ++i) {
                 mbar_expect_tx(&full_bar[i], W_BYTES + X_BYTES);
-                tma_load_2d(smem_w + i * W_BYTES, &tmap_w, &full_bar[i], (kb0 + i) * kGemmBK, n_t * kSkinnyBF,
+                tma_load_2d(smem_w + i * W_BYTES, &tmap_w, &full_bar[i], (kb0 + i) * KB, n_t * kSkinnyBF,
                             kEvictFirst);
             }
             griddep_wait();
             for (int i = 0; i < pre; ++i)
-                tma_load_2d(smem_x + i * X_BYTES, &tmap_x, &full_bar[i], (kb0 + i) * kGemmBK, 0, kEvictLast);
+                tma_load_2d(smem_x + i * X_BYTES, &tmap_x, &full_bar[i], (kb0 + i) * KB, 0, kEvictLast);
             uint32_t stage = 0, phase = 1;  // the ring has been filled once
             for (int kb = kb0 + pre; kb < kb1; ++kb) {
                 mbar_wait(&empty_bar[stage], phase ^ 1);
                 mbar_expect_tx(&full_bar[stage], W_BYTES + X_BYTES);
-                tma_load_2d(smem_x + stage * X_BYTES, &tmap_x, &full_bar[stage], kb * kGemmBK, 0, kEvictLast);
-                tma_load_2d(smem_w + stage * W_BYTES, &tmap_w, &full_bar[stage], kb * kGemmBK, n_t * kSkinnyBF,
+                tma_load_2d(smem_x + stage * X_BYTES, &tmap_x, &full_bar[stage], kb * KB, 0, kEvictLast);
+                tma_load_2d(smem_w + stage * W_BYTES, &tmap_w, &full_bar[stage], kb * KB, n_t * kSkinnyBF,
                             kEvictFirst);
                 if (++stage == STAGES) {
                     stage = 0;
@@ -175,8 +181,10 @@ gemm_skinny_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_cons
                 const uint64_t dw = make_desc_kmajor_sw128(smem_u32(smem_w + stage * W_BYTES));
                 const uint64_t dx = make_desc_kmajor_sw128(smem_u32(smem_x + stage * X_BYTES));
 #pragma unroll
-                for (int k = 0; k < kGemmBK / 16; ++k)
-                    umma_f16_ss(tmem_base, dw + 2 * k, dx + 2 * k, IDESC, (kb > kb0 || k > 0) ? 1u : 0u);
+                for (int k = 0; k < 4; ++k) {  // 32 bytes of K per instruction: 16 (16-bit) or 32 (fp8) elements
+                    if constexpr (kFp8) umma_f8_ss(tmem_base, dw + 2 * k, dx + 2 * k, IDESC, (kb > kb0 || k > 0) ? 1u : 0u);
+                    else umma_f16_ss(tmem_base, dw + 2 * k, dx + 2 * k, IDESC, (kb > kb0 || k > 0) ? 1u : 0u);
+                }
                 umma_commit(&empty_bar[stage]);
                 if (++stage == STAGES) {
                     stage = 0;
@@ -193,6 +201,11 @@ gemm_skinny_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_cons
         tc_fence_after();
         float v[NT];
         skinny_tmem_load<NT>(tmem_base + ((quad * 32u) << 16), v);
+        if constexpr (kFp8) {
+            const float sw = n < args.N ? __ldg(args.w_scale + n) : 0.0f;
+#pragma unroll
+            for (int t = 0; t < NT; ++t) v[t] *= sw * (t < args.M ? __ldg(args.a_scale + t) : 0.0f);
+        }
         if constexpr (EPI == EPI_RED_F32) {
             if (n < args.N) {
                 const float b = (args.bias != nullptr && sp == 0) ? load_scalar<kBf16>(args.bias, n) : 0.0f;

@@ -430,9 +430,12 @@ def quantize_fp8_rows(x: torch.Tensor, q: Optional[torch.Tensor] = None,
 
 
 def gemm_fp8(aq: torch.Tensor, a_scale: torch.Tensor, wq: torch.Tensor, w_scale: torch.Tensor, out: torch.Tensor,
-             bias: Optional[torch.Tensor] = None, act: int = ACT_IDENTITY, gated: bool = False, bn: int = 0) -> torch.Tensor:
+             bias: Optional[torch.Tensor] = None, act: int = ACT_IDENTITY, gated: bool = False, bn: int = 0,
+             workspace: Optional[torch.Tensor] = None, splits: int = 0) -> torch.Tensor:
     """``out = epilogue((aq @ wq.T) * a_scale[:, None] * w_scale[None, :] + bias)`` with E4M3 operands on
-    ``tcgen05.mma.kind::f8f6f4`` (fp32 accumulation in TMEM). ``aq``: [M, K] uint8, ``wq``: [N, K] uint8."""
+    ``tcgen05.mma.kind::f8f6f4`` (fp32 accumulation in TMEM). ``aq``: [M, K] uint8, ``wq``: [N, K] uint8.
+    M <= 64 with ``bn == 0`` takes the feature-major weight-streaming kernel (split-K through ``workspace``, a zeroed
+    uint8 buffer of at least :func:`gemm_fp8_skinny_workspace_bytes`)."""
     _check_2d(aq, "aq")
     _check_2d(wq, "wq")
     _check_2d(out, "out")
@@ -440,12 +443,40 @@ def gemm_fp8(aq: torch.Tensor, a_scale: torch.Tensor, wq: torch.Tensor, w_scale:
     N = wq.shape[0]
     assert wq.shape[1] == K and aq.dtype == torch.uint8 and wq.dtype == torch.uint8
     assert a_scale.dtype == torch.float32 and w_scale.dtype == torch.float32
-    rc = native.cuda_lib().hds_gemm_fp8(_p(aq), aq.stride(0), _p(a_scale), _p(wq), wq.stride(0), _p(w_scale), M, N, K,
-                                        _dt(out), EPI_GATED if gated else EPI_STORE, act, _p(bias), _p(out), out.stride(0),
-                                        bn, _stream())
-    native.check(rc, "hds_gemm_fp8")
+    lib = native.cuda_lib()
+    if M <= 64 and bn == 0:
+        rc = lib.hds_gemm_fp8_skinny(_p(aq), aq.stride(0), _p(a_scale), _p(wq), wq.stride(0), _p(w_scale), M, N, K, _dt(out),
+                                     EPI_GATED if gated else EPI_STORE, act, _p(bias), _p(out), out.stride(0), None, 0,
+                                     _p(workspace), 0 if workspace is None else workspace.numel(), splits, _stream())
+        native.check(rc, "hds_gemm_fp8_skinny")
+    else:
+        rc = lib.hds_gemm_fp8(_p(aq), aq.stride(0), _p(a_scale), _p(wq), wq.stride(0), _p(w_scale), M, N, K, _dt(out),
+                              EPI_GATED if gated else EPI_STORE, act, _p(bias), _p(out), out.stride(0), bn, _stream())
+        native.check(rc, "hds_gemm_fp8")
     _count()
     return out
+
+
+def gemm_fp8_skinny_workspace_bytes(M: int, N: int) -> int:
+    nt = 16 if M <= 16 else 32 if M <= 32 else 64
+    n_tiles = (N + 127) // 128
+    return ((n_tiles * 128 * nt * 4 + 255) & ~255) + n_tiles * 16
+
+
+def gemm_fp8_accum(aq: torch.Tensor, a_scale: torch.Tensor, wq: torch.Tensor, w_scale: torch.Tensor, accum: torch.Tensor,
+                   bias: Optional[torch.Tensor] = None, out_dtype: torch.dtype = torch.bfloat16, splits: int = 0) -> torch.Tensor:
+    """``accum (fp32) += (aq @ wq.T) * scales (+ bias once)`` for M <= 64 (decode): split-K partial sums go straight
+    into ``accum`` with fp32 atomics, no scratch."""
+    M, K = aq.shape
+    N = wq.shape[0]
+    assert accum.dtype == torch.float32 and M <= 64
+    dt = 0 if out_dtype == torch.bfloat16 else 1
+    rc = native.cuda_lib().hds_gemm_fp8_skinny(_p(aq), aq.stride(0), _p(a_scale), _p(wq), wq.stride(0), _p(w_scale), M, N, K, dt,
+                                               2, ACT_IDENTITY, _p(bias), None, 0, _p(accum), accum.stride(0), None, 0, splits,
+                                               _stream())
+    native.check(rc, "hds_gemm_fp8_skinny")
+    _count()
+    return accum
 
 
 def moe_gather(y: torch.Tensor, mapped_slots: torch.Tensor, scores: torch.Tensor, out: torch.Tensor) -> None:

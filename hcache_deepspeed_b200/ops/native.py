@@ -57,6 +57,7 @@ def _declare_cuda(lib: ctypes.CDLL) -> None:
         "hds_moe_gather": [P, L, P, P, P, L, I, I, I, I, P],
         "hds_gemm_2sm": [P, L, P, L, I, I, I, I, I, I, P, P, L, I, P],
         "hds_quantize_fp8_rows": [P, L, I, I, I, P, L, P, P],
+        "hds_gemm_fp8_skinny": [P, L, P, P, L, P, I, I, I, I, I, I, P, P, L, P, L, P, L, I, P],
         "hds_gemm_fp8": [P, L, P, P, L, P, I, I, I, I, I, I, P, P, L, I, P],
         "hds_quantize_int": [P, I, L, I, I, I, P, P, P],
         "hds_dequantize_int": [P, P, L, I, I, P, I, P],

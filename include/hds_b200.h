@@ -225,6 +225,14 @@ int hds_gemm_fp8(const void* Aq, int64_t lda, const float* a_scale, const void* 
                  int M, int N, int K, int out_dtype, int epilogue, int act, const void* bias, void* out, int64_t ldo,
                  int bn, void* stream);
 
+/* Decode-size (M <= 64) E4M3 GEMM on the feature-major weight-streaming kernel: epilogue 0 store / 1 gated (into out) or
+ * 2 fp32 accumulate (accum[m, n] += ..., bias added once). Split-K for store / gated needs a zeroed scratch of
+ * hds_gemm_fp8_skinny_workspace_bytes(M, N) bytes (left zeroed); splits 0 = auto. lda / ldw in bytes. */
+int64_t hds_gemm_fp8_skinny_workspace_bytes(int M, int N);
+int hds_gemm_fp8_skinny(const void* Aq, int64_t lda, const float* a_scale, const void* Wq, int64_t ldw, const float* w_scale,
+                        int M, int N, int K, int out_dtype, int epilogue, int act, const void* bias, void* out, int64_t ldo,
+                        float* accum, int64_t ld_accum, void* ws, int64_t ws_bytes, int splits, void* stream);
+
 /* CTA-pair GEMM (tcgen05 cta_group::2, 256 x bn tiles over two SMs): out = epilogue(A W^T + bias), 16-bit operands.
  * Arguments as hds_gemm (no split-K); bn: 0 = auto, 128 or 256. hds_gemm_fp8 reaches the same kernel with bn = 0
  * (auto, M > 128) or bn = 1128 / 1256. */

@@ -123,3 +123,35 @@ def test_gemm_fp8(dtype, M, N, Kd, mode, bn):
     full = a.float() @ w.float().t() + bias.float()
     if not gated:
         assert (out.float() - full).abs().mean() < 0.05 * full.abs().mean() + 0.02
+
+
+@pytest.mark.parametrize("M", [1, 8, 16, 33, 64])
+@pytest.mark.parametrize("mode", ["store", "gated", "accum"])
+@pytest.mark.parametrize("use_ws", [False, True])
+def test_gemm_fp8_skinny(M, mode, use_ws):
+    """Decode-size E4M3 GEMM on the feature-major kernel: ragged N / K, every token tile, split-K through scratch
+    (left zeroed) or straight into the fp32 accumulator."""
+    from hcache_deepspeed_b200.ops import kernels as K
+    torch.manual_seed(M)
+    N, Kd = (690 if mode == "gated" else 1000), 2128
+    a = torch.randn(M, Kd, device="cuda").bfloat16()
+    w = (torch.randn(N, Kd, device="cuda") * Kd ** -0.5).bfloat16()
+    bias = torch.randn(N, device="cuda").bfloat16()
+    aq, a_s = K.quantize_fp8_rows(a)
+    wq, w_s = K.quantize_fp8_rows(w)
+    want = (aq.view(torch.float8_e4m3fn).float() * a_s[:, None]) @ (wq.view(torch.float8_e4m3fn).float() * w_s[:, None]).t() \
+        + bias.float()
+    ws = torch.zeros(K.gemm_fp8_skinny_workspace_bytes(M, N), dtype=torch.uint8, device="cuda") if use_ws else None
+    for rep in range(2):
+        if mode == "accum":
+            acc = torch.full((M, N), 0.5, device="cuda", dtype=torch.float32)
+            K.gemm_fp8_accum(aq, a_s, wq, w_s, acc, bias=bias)
+            torch.testing.assert_close(acc, want + 0.5, rtol=2e-3, atol=2e-3)
+        else:
+            gated = mode == "gated"
+            out = torch.empty(M, N // 2 if gated else N, dtype=torch.bfloat16, device="cuda")
+            K.gemm_fp8(aq, a_s, wq, w_s, out, bias=bias, act=K.ACT_SILU if gated else K.ACT_IDENTITY, gated=gated, workspace=ws)
+            ref_out = torch.nn.functional.silu(want[:, 0::2]) * want[:, 1::2] if gated else want
+            torch.testing.assert_close(out.float(), ref_out, rtol=2e-2, atol=2e-2)
+    if ws is not None:
+        assert int(ws.view(torch.int32).abs().max()) == 0
