@@ -45,7 +45,7 @@ def parse():
     p.add_argument("--quant", default="none", choices=["none", "wf8af8"],
                    help="none (default, the bf16 headline configuration) or wf8af8: E4M3 weights + per-token fp8 activations; "
                         "reported with dtype fp8-w8a8 and NOT comparable with the bf16 baseline")
-    p.add_argument("--plan", default="hidden", choices=["auto", "hidden"],
+    p.add_argument("--plan", default="hidden", choices=["auto", "hidden", "planner"],
                    help="hidden: every layer from hidden states (fastest measured on 1xB200: 20.4 ms vs 21.6 ms); auto: planner mix with a recomputed prefix")
     return p.parse_args()
 
@@ -146,10 +146,18 @@ def run_ours(a):
     torch.cuda.synchronize()
     eng.flush(10 ** 9)
     prefill_s = p0.elapsed_time(p1) / 1e3
-    plan = plan_restore(spec, ctx, LinkModel(tp_size=tp), allow_kv=False, allow_recompute=(a.plan == "auto"),
-                        extra_compute_s=prefill_s)
-    hidden_layers, recompute_layers = plan.layers_of("hidden"), plan.layers_of("none")
-    lat_hidden = latents[hidden_layers[0]:] if hidden_layers else None  # the plan keeps a suffix of layers
+    # planner: hidden states vs offloaded KV pages per layer by bytes moved (GQA models: KV is smaller than the hidden state)
+    plan = plan_restore(spec, ctx, LinkModel(tp_size=tp), allow_kv=(a.plan == "planner" and tp == 1),
+                        allow_recompute=(a.plan == "auto"), extra_compute_s=prefill_s)
+    hidden_layers, recompute_layers, kv_layers = plan.layers_of("hidden"), plan.layers_of("none"), plan.layers_of("kv")
+    lat_hidden = latents[hidden_layers[0]:hidden_layers[-1] + 1] if hidden_layers else None  # a contiguous run of layers
+    kv_pages = None
+    if kv_layers:
+        bs_kv = model._state_manager.kv_block_size
+        n_blk = (ctx + bs_kv - 1) // bs_kv
+        kv_pages = torch.empty((len(kv_layers), n_blk, 2, spec.n_kv_heads, bs_kv, spec.head_dim), dtype=torch.bfloat16,
+                               pin_memory=True)
+        kv_pages.copy_((torch.randn(kv_pages.shape, generator=g) * 0.3).to(torch.bfloat16))
     interleave = plan.interleave
     # tensor parallel: every rank keeps (and transfers) only its 1/tp row slice of the hidden states; the restore
     # kernels gather the slices from peer HBM over NVLink (needs the fused/symmetric-memory communicator)
@@ -158,7 +166,8 @@ def run_ours(a):
         lo, hi = eng.latent_row_range(ctx)
         lat_slice = latents[:, lo:hi].contiguous().pin_memory()
     rows_moved = (hi - lo) if sharded else ctx
-    h2d_step = B * (len(hidden_layers) * rows_moved * spec.hidden * 2 + ctx * 4 + n_new * 4) + B * D * 4
+    h2d_step = B * (len(hidden_layers) * rows_moved * spec.hidden * 2 + ctx * 4 + n_new * 4) + B * D * 4 + \
+        B * (kv_pages.numel() * 2 if kv_pages is not None else 0)
     d2h_step = B * (D + 1) * 4
 
     ev = lambda: torch.cuda.Event(enable_timing=True)  # noqa: E731
@@ -174,8 +183,9 @@ def run_ours(a):
             if sharded:
                 eng.restore_kv([uid], [ctx_tokens], [lat_slice], do_checks=False, sharded=True)
             else:
-                eng.restore_session(uid, ctx_tokens, hidden=lat_hidden, hidden_layers=hidden_layers,
-                                    recompute_layers=recompute_layers, interleave=interleave)
+                eng.restore_session(uid, ctx_tokens, hidden=lat_hidden, hidden_layers=hidden_layers, kv=kv_pages,
+                                    kv_layers=kv_layers, kv_layer_major=True, recompute_layers=recompute_layers,
+                                    interleave=interleave)
             logits, _ = eng.put([uid], [new_tokens[i]], do_checks=False)
             tok = kernels.argmax(logits)
             tok_host = tok.cpu()  # D2H of the first token: the TTFT point
@@ -246,7 +256,7 @@ def run_ours(a):
                        "numa_bound_cpus": len(numa_cpus),
                        "restore_plan": {"recompute_prefix_layers": 0 if sharded else len(recompute_layers),
                                         "hidden_state_layers": spec.n_layers if sharded else len(hidden_layers),
-                                        "kv_offload_layers": 0, "tp_sharded_restore": sharded,
+                                        "kv_offload_layers": 0 if sharded else len(kv_layers), "tp_sharded_restore": sharded,
                                         "tp_collectives": "fused GEMM-epilogue reduction" if bool(getattr(model.comm, "fused", False))
                                         else ("nccl" if tp > 1 else "none")},
                        "l2_policy": f"working set per step (weights {model.w.n_bytes() / 2**30:.1f} GiB + KV) exceeds the 126 MB L2"},

@@ -159,12 +159,14 @@ class InferenceEngineV2:
     def restore_session(self, uid: int, tokens: torch.Tensor, hidden: Optional[torch.Tensor] = None,
                         hidden_layers: Sequence[int] = (), kv: Optional[torch.Tensor] = None,
                         kv_layers: Sequence[int] = (), recompute_layers: Sequence[int] = (),
-                        defer: Optional[bool] = None, interleave: float = 2.5) -> None:
+                        defer: Optional[bool] = None, interleave: float = 2.5, kv_layer_major: bool = False) -> None:
         """Bring one session's context back following a mixed plan (``hcache/planner.py``):
 
         * ``recompute_layers`` — must be the prefix ``0..r-1``: recomputed from ``tokens`` (uses the GPU while the
           host link is the bottleneck);
-        * ``kv_layers`` — ``kv [n_blocks, len(kv_layers), 2, kv_heads, block, head_dim]`` copied into the pages;
+        * ``kv_layers`` — ``kv [n_blocks, len(kv_layers), 2, kv_heads, block, head_dim]`` copied into the pages; with
+          ``kv_layer_major`` the tensor is ``[len(kv_layers), n_blocks, ...]`` and streams layer by layer, overlapped
+          with the next forward like the hidden states;
         * ``hidden_layers`` — ``hidden [len(hidden_layers), n_tokens, hidden]`` through the K/V projection kernel.
 
         ``interleave``: saved layers projected per recomputed layer (layer-forward time / per-layer transfer time).
@@ -193,7 +195,8 @@ class InferenceEngineV2:
         if n_hidden:
             model.restore_kv(self._batch, [hidden], layers=list(hidden_layers), defer=True)
         if len(list(kv_layers)):
-            model.restore_kv_pages(seq.all_block_ids, kv, list(kv_layers))
+            model.restore_kv_pages(seq.all_block_ids, kv, list(kv_layers), defer=bool(defer) and kv_layer_major,
+                                   layer_major=kv_layer_major)
         if rl:
             model.forward(self._batch, capture=False, n_layers_limit=len(rl), restore_interleave=interleave)
         if n_hidden and not defer:

@@ -102,6 +102,8 @@ class RaggedTransformer:
         self._state_config = state_config
         self._state_manager: Optional[DSStateManager] = None
         self._pending_restore = None
+        self._pending_kv = None      # deferred layer-pipelined reload of offloaded KV pages
+        self._kv_stage = None
         self.capture_enabled = capture_latents
         self.n_q, self.n_kv, self.d = self.info.n_q, self.info.n_kv, spec.head_dim
         self.scale = spec.attn_scale if spec.attn_scale is not None else ref.attention_scale(spec.head_dim)
@@ -434,6 +436,8 @@ class RaggedTransformer:
             self._norm(resid, lw.norm1_g, xn, beta=lw.norm1_b, delta=pending,
                        res_out=resid if pending is not None else None)
             kv_layer = kv.get_cache(li)
+            if self._pending_kv is not None:
+                self._kv_step(li)       # deferred reload of this layer's offloaded KV pages
             if self._pending_restore is not None:
                 self._restore_step(li)  # deferred HCache restore: this layer's K/V must land before its attention
             ops.qkv_rope_kv_append(xn, lw.w_qkv, lw.b_qkv, self.qkv_buf[:T], self.q_buf[:T], kv_layer, pos, slot,
@@ -466,7 +470,7 @@ class RaggedTransformer:
                 for b in self._delta_bufs:
                     b[:T].zero_()
             return None, (self.latent_buf[:n_run, :T] if capture else None)
-        if self._pending_restore is not None:
+        if self._pending_restore is not None or self._pending_kv is not None:
             self.finish_pending_restore()
         # ---- last-token logits ----
         fin = self.xn2[:T]
@@ -620,6 +624,11 @@ class RaggedTransformer:
 
     def finish_pending_restore(self) -> None:
         """Run whatever is left of a deferred restore now (compute stream)."""
+        kvst = self._pending_kv
+        if kvst is not None:
+            while kvst["done"] < len(kvst["layers"]):
+                self._kv_apply(kvst, kvst["done"])
+            self._pending_kv = None
         st = self._pending_restore
         if st is None:
             return
@@ -627,15 +636,76 @@ class RaggedTransformer:
             self._restore_project(st, st["done"])
         self._pending_restore = None
 
-    def restore_kv_pages(self, block_ids: torch.Tensor, kv_host: torch.Tensor, layers: Sequence[int]) -> None:
-        """Plain KV reload for the layers the planner assigned to KV offload: ``kv_host`` is
-        ``[n_blocks, len(layers), 2, kvh, bs, d]`` (host), written into ``block_ids`` of each listed layer."""
+    # ---- layer-pipelined reload of offloaded KV pages ----------------------------------------------------------
+    def _kv_issue(self, st) -> None:
+        """Queue the H2D of the next offloaded layer into its staging slot (IO stream)."""
+        j = st["issued"]
+        k = j % RESTORE_SLOTS
+        io = self.io_stream
+        with torch.cuda.stream(io):
+            if j >= RESTORE_SLOTS:
+                io.wait_event(self._kv_ev_consumed[k])
+            self._kv_stage[k][:st["n_blocks"]].copy_(st["kv"][j], non_blocking=True)
+            self._kv_ev_loaded[k].record(io)
+        st["issued"] = j + 1
+
+    def _kv_apply(self, st, j: int) -> None:
+        """Scatter staged layer ``j`` into its KV blocks (compute stream) and keep the IO stream ahead."""
+        k = j % RESTORE_SLOTS
+        li = st["layers"][j]
+        comp = torch.cuda.current_stream()
+        comp.wait_event(self._kv_ev_loaded[k])
+        cache = self._state_manager.kv_cache.full_cache
+        self.ops.k.kv_blocks_copy(cache[li:li + 1], self._kv_stage[k][:st["n_blocks"]].unsqueeze(1), st["ids"], to_staging=False)
+        self._kv_ev_consumed[k].record(comp)
+        st["done"] = j + 1
+        if st["issued"] < len(st["layers"]):
+            self._kv_issue(st)
+
+    def _kv_step(self, li: int) -> None:
+        """Called by ``forward`` right before layer ``li`` reads its KV cache."""
+        st = self._pending_kv
+        j = st["by_layer"].get(li)
+        if j is not None:
+            while st["done"] <= j:
+                self._kv_apply(st, st["done"])
+        if st["done"] >= len(st["layers"]):
+            self._pending_kv = None
+
+    def restore_kv_pages(self, block_ids: torch.Tensor, kv_host: torch.Tensor, layers: Sequence[int], defer: bool = False,
+                         layer_major: bool = False) -> None:
+        """KV reload for the layers the planner assigned to KV offload, written into ``block_ids`` of each listed layer.
+        ``kv_host`` is ``[n_blocks, len(layers), 2, kvh, bs, d]`` (one bulk transfer), or with ``layer_major``
+        ``[len(layers), n_blocks, 2, kvh, bs, d]``: every layer is then one contiguous transfer, streamed through
+        ``RESTORE_SLOTS`` staging slots; with ``defer`` layer ``l`` is scattered by the next ``forward`` right before its
+        own layer ``l``, so the new turn's prefill overlaps the transfers exactly as it does for hidden states."""
         kv = self._state_manager.kv_cache
         cache = kv.full_cache
         ids = block_ids.to(torch.int32)
         if self.device.type != "cuda":
             for j, li in enumerate(layers):
-                cache[li, ids.long()] = kv_host[:, j].to(cache.dtype)
+                cache[li, ids.long()] = (kv_host[j] if layer_major else kv_host[:, j]).to(cache.dtype)
+            return
+        if layer_major:
+            if self._pending_kv is not None:        # (a pending HIDDEN-state restore of the same plan stays deferred)
+                prev = self._pending_kv
+                while prev["done"] < len(prev["layers"]):
+                    self._kv_apply(prev, prev["done"])
+                self._pending_kv = None
+            n_blocks = int(kv_host.shape[1])
+            shape = tuple(kv_host.shape[2:])
+            if self._kv_stage is None or self._kv_stage.shape[1] < n_blocks or tuple(self._kv_stage.shape[2:]) != shape:
+                self._kv_stage = torch.empty((RESTORE_SLOTS, n_blocks) + shape, dtype=cache.dtype, device=self.device)
+                self._kv_ev_loaded = [torch.cuda.Event() for _ in range(RESTORE_SLOTS)]
+                self._kv_ev_consumed = [torch.cuda.Event() for _ in range(RESTORE_SLOTS)]
+            self.io_stream.wait_stream(torch.cuda.current_stream())   # slots may still feed an earlier restore's copies
+            st = {"layers": list(layers), "kv": kv_host, "ids": ids.to(self.device, non_blocking=True), "n_blocks": n_blocks,
+                  "issued": 0, "done": 0, "by_layer": {li: j for j, li in enumerate(layers)}}
+            self._pending_kv = st
+            for _ in range(min(RESTORE_SLOTS, len(st["layers"]))):
+                self._kv_issue(st)
+            if not defer:
+                self.finish_pending_restore()
             return
         ids_dev = ids.to(self.device, non_blocking=True)
         comp = torch.cuda.current_stream()

@@ -189,3 +189,34 @@ def test_fp8_engine_mode_gpu():
     for _ in range(3):
         a, _ = eng.put([1, 2], [nxt, nxt], capture_latents=False)
     assert torch.isfinite(a.float()).all()
+
+
+@pytest.mark.parametrize("kinds", [["kv"] * 6, ["hidden", "hidden", "hidden", "kv", "kv", "kv"], ["none", "hidden", "kv", "kv", "kv", "kv"]])
+def test_layer_pipelined_kv_reload(kinds):
+    """Mixed restore plans with offloaded KV pages streamed layer by layer (layer-major host tensor, deferred into the next
+    put) reproduce the live session's logits; more KV layers than staging slots exercises slot reuse."""
+    from hcache_deepspeed_b200.inference.v2 import build_engine_from_arch
+    from hcache_deepspeed_b200.models.arch import named_arch
+    spec = named_arch("llama-2-7b").scaled(n_layers=6)
+    eng = build_engine_from_arch(spec, _cfg(T=1024, ctx=2048, mem=1 << 30), seed=4, device=torch.device("cuda"))
+    g = torch.Generator().manual_seed(0)
+    toks = torch.randint(0, spec.vocab, (700, ), generator=g)
+    _, lat = eng.put([1], [toks])
+    seq = eng.state_manager.get_sequence(1)
+    hl = [i for i, k in enumerate(kinds) if k == "hidden"]
+    kl = [i for i, k in enumerate(kinds) if k == "kv"]
+    rl = [i for i, k in enumerate(kinds) if k == "none"]
+    kv = eng.state_manager.kv_cache.offload_layers(seq.all_block_ids, kl)          # [n_blocks, len(kl), 2, kvh, bs, d] on host
+    kv_major = kv.transpose(0, 1).contiguous().pin_memory()
+    turn = torch.randint(0, spec.vocab, (40, ), generator=g)
+    for uid, defer in ((10, False), (11, True)):
+        eng.restore_session(uid, toks, hidden=lat[0][hl] if hl else None, hidden_layers=hl, kv=kv_major, kv_layers=kl,
+                            kv_layer_major=True, recompute_layers=rl, defer=defer)
+    want, _ = eng.put([1], [turn], capture_latents=False)
+    for uid in (10, 11):
+        got, _ = eng.put([uid], [turn], capture_latents=False)
+        torch.testing.assert_close(got.float(), want.float(), rtol=3e-2, atol=3e-2)
+    eng.restore_session(12, toks, hidden=lat[0][hl] if hl else None, hidden_layers=hl, kv=kv_major, kv_layers=kl,
+                        kv_layer_major=True, recompute_layers=rl, defer=True)
+    eng.flush(12)                                    # never followed by a forward: flush completes the transfers
+    torch.cuda.synchronize()

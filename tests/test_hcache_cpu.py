@@ -114,7 +114,9 @@ def test_mixed_plan_restore_equals_live(arch):
             continue
         kv = eng.state_manager.kv_cache.offload_layers(seq.all_block_ids, kl) if kl else None
         uid = 100 + len(hl) * 10 + len(kl) + (50 if kinds[0] == "kv" else 0)
-        eng.restore_session(uid, toks, hidden=lat[0][hl] if hl else None, hidden_layers=hl, kv=kv, kv_layers=kl,
+        major = bool(kl) and kinds[-1] == "kv"    # also exercise the layer-major (per-layer streaming) KV layout
+        eng.restore_session(uid, toks, hidden=lat[0][hl] if hl else None, hidden_layers=hl,
+                            kv=kv.transpose(0, 1).contiguous() if major else kv, kv_layers=kl, kv_layer_major=major,
                             recompute_layers=rl)
         probe = torch.randint(0, spec.vocab, (3, ), generator=g)
         la, _ = eng.put([1], [probe], capture_latents=False)
