@@ -222,13 +222,29 @@ MAX_PREFILL_SPLITS = 16
 
 
 def pick_decode_splits(n_items: int, n_kv_heads: int, max_kv_len: int) -> int:
-    """KV splits for the split-KV kernel: split only while (items x kv heads x splits) stays within one CTA per SM —
-    measured (profiles/kernel_bench_attn_warps.txt): 32 CTAs -> 4 splits, 64 -> 2, >= 128 -> none; each split keeps at
-    least 2 tiles (256 keys)."""
+    """KV splits for the split-KV kernel. Up to one CTA per SM: split until (items x kv heads x splits) fills the SMs —
+    measured (profiles/kernel_bench_attn_warps.txt): 32 CTAs -> 4 splits, 64 -> 2. Up to the 2 x 148 resident slots of
+    the 4-warp configuration: one wave, no split. Beyond that a second, mostly empty wave would cost up to half the
+    bandwidth (320 CTAs: 3.8 TB/s unsplit vs 5.1 TB/s with 4 splits, profiles/kernel_bench_attn_waves.txt): take the
+    smallest split count whose waves are at least 85 % full. Each split keeps at least 2 tiles (256 keys)."""
     ctas = max(1, n_items * n_kv_heads)
-    want = max(1, N_SM // ctas)
     tiles = max(1, (max_kv_len + 127) // 128)
-    return int(max(1, min(want, MAX_DECODE_SPLITS, tiles // 2 if tiles >= 2 else 1)))
+    cap = max(1, min(MAX_DECODE_SPLITS, tiles // 2 if tiles >= 2 else 1))
+    slots = 2 * N_SM
+    if ctas <= N_SM:
+        want = max(1, N_SM // ctas)
+    elif ctas <= slots:
+        want = 1
+    else:
+        want, best = 1, 0.0
+        for s in range(1, min(cap, 8) + 1):
+            eff = ctas * s / (slots * -(-ctas * s // slots))
+            if eff >= 0.85:
+                want = s
+                break
+            if eff > best:
+                want, best = s, eff
+    return int(max(1, min(want, cap)))
 
 
 def pick_prefill_splits(n_items: int, n_q_heads: int, max_kv_len: int) -> int:

@@ -151,7 +151,11 @@ def bench_restore():
 
 def bench_attention_decode():
     d, bs = 128, 64
-    for (n_seqs, ctx, nq, nkv) in [(8, 4096, 32, 32), (16, 4096, 32, 32), (64, 4096, 32, 32), (8, 16384, 32, 32), (64, 4096, 8, 1), (1, 4096, 32, 32), (4, 4096, 32, 32)]:
+    shapes = [(8, 4096, 32, 32), (16, 4096, 32, 32), (64, 4096, 32, 32), (8, 16384, 32, 32), (64, 4096, 8, 1), (1, 4096, 32, 32), (4, 4096, 32, 32)]
+    sweep = (1, 2, 4, 8, 16)
+    if os.environ.get("ATTN_SWEEP"):   # wave-quantisation study: more CTAs than resident slots, every split count
+        shapes, sweep = [(8, 4096, 32, 32), (8, 4096, 40, 40), (12, 4096, 32, 32)], tuple(range(1, 11))
+    for (n_seqs, ctx, nq, nkv) in shapes:
         blocks_per_seq = (ctx + 1 + bs - 1) // bs
         nb = n_seqs * blocks_per_seq
         cache = (torch.randn(nb, 2, nkv, bs, d, device=dev) * 0.3).to(torch.bfloat16)
@@ -161,8 +165,8 @@ def bench_attention_decode():
         out = torch.empty_like(q)
         G = nq // nkv
         kv_bytes = n_seqs * (ctx + 1) * 2 * nkv * d * 2
-        for splits in (1, 2, 4, 8, 16):
-            if n_seqs * nkv * splits > 148 * 16:
+        for splits in sweep:
+            if n_seqs * nkv * splits > 148 * 32:
                 continue
             ws = torch.zeros(max(16, K.splitkv_workspace_bytes(n_seqs, nq, nkv, d, splits, G)), dtype=torch.uint8, device=dev)
             med, mn = timeit(lambda: K.paged_attention_splitkv(q, out, cache, tables, items, n_seqs, G, nq, nkv, d, bs, splits,
