@@ -176,8 +176,21 @@ static int launch_skinny(int epi, bool bf16, const void* X, int64_t ldx, const v
         if (want_splits > 0) {
             splits = want_splits;
         } else {
+            // measured (profiles/kernel_bench_decode_gemm.jsonl, BIG_SHAPES run): fill the resident slots once; past one full
+            // wave of tiles, split until the waves are >= 80 % full (448 tiles of a 57344-wide MLP-1: 5.25 -> 5.66 TB/s at 4 splits)
             const int slots = sm_count() * skinny_occupancy(nt);
             splits = slots / n_tiles;
+            if (n_tiles > slots) {
+                splits = 1;
+                for (int s = 1; s <= 8; ++s) {
+                    const int64_t ctas = static_cast<int64_t>(n_tiles) * s;
+                    const int64_t waves = (ctas + slots - 1) / slots;
+                    if (ctas * 100 >= waves * slots * 80) {
+                        splits = s;
+                        break;
+                    }
+                }
+            }
             if (splits > kb_total / 4) splits = kb_total / 4;
             if (splits > 8) splits = 8;
         }

@@ -80,9 +80,13 @@ def bench_gemm():
 
 
 def bench_decode_gemm():
-    for M in (8, 32, 64):
-        for (N, Kd, kind) in [(12288, 4096, "store"), (22016, 4096, "gated"), (4096, 4096, "accum"), (4096, 11008, "accum"),
-                              (32000, 4096, "store")]:
+    shapes = [(12288, 4096, "store"), (22016, 4096, "gated"), (4096, 4096, "accum"), (4096, 11008, "accum"), (32000, 4096, "store")]
+    ms = (8, 32, 64)
+    if os.environ.get("BIG_SHAPES"):   # Llama-2-70B / 13B layer shapes at decode size: wave quantisation of the feature tiles
+        shapes = [(57344, 8192, "gated"), (10240, 8192, "store"), (8192, 28672, "accum"), (27648, 5120, "gated"), (15360, 5120, "store")]
+        ms = (8, )
+    for M in ms:
+        for (N, Kd, kind) in shapes:
             a, w = rand(M, Kd), rand(N, Kd, scale=Kd ** -0.5)
             wbytes = N * Kd * 2
             if kind == "accum":
