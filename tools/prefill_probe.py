@@ -18,7 +18,8 @@ cfg = RaggedInferenceEngineConfig(
     state_manager={"max_tracked_sequences": 16, "max_ragged_batch_size": n_tok + 64, "max_ragged_sequence_count": 8,
                    "max_context": n_tok + 256,
                    "memory_config": {"mode": "allocate", "size": int(3 * (n_tok + 256) * spec.kv_bytes_per_token_layer() * spec.n_layers)}},
-    hcache={"enabled": True, "capture": "off"})
+    hcache={"enabled": True, "capture": "off"},
+    quantization={"quantization_mode": os.environ.get("PROBE_QUANT") or None})
 eng = build_engine_from_arch(spec, cfg, seed=1234, dtype=torch.bfloat16, device=dev)
 g = torch.Generator().manual_seed(3)
 toks = torch.randint(0, spec.vocab, (n_tok, ), generator=g).pin_memory()
@@ -36,4 +37,5 @@ for i in range(8):
 steady = sorted(times[3:])
 print(json.dumps({"case": "fresh_prefill", "model": "llama-2-7b", "tokens": n_tok, "ms_median": round(steady[len(steady) // 2], 3),
                   "ms_min": round(steady[0], 3), "tokens_per_s": round(n_tok / steady[len(steady) // 2] * 1e3, 1),
-                  "gemm_2sm": os.environ.get("HDS_GEMM_2SM", "1")}))
+                  "gemm_2sm": os.environ.get("HDS_GEMM_2SM", "1"),
+                  "quant": os.environ.get("PROBE_QUANT", "none")}))
