@@ -45,7 +45,8 @@ class HCacheSessionManager:
         st = self.store.load(uid)
         plan = self.plan_for(st.n_tokens)
         self.engine.restore_session(uid, st.tokens, hidden=st.hidden, hidden_layers=st.layers_of("hidden"), kv=st.kv,
-                                    kv_layers=st.layers_of("kv"), recompute_layers=st.layers_of("none"),
+                                    kv_layers=st.layers_of("kv"), kv_layer_major=st.kv_layer_major,
+                                    recompute_layers=st.layers_of("none"),
                                     interleave=plan.interleave or 2.5)
         self._resident.add(uid)
         # the hidden states of restored layers are already known: carry them into the next save
@@ -123,13 +124,14 @@ class HCacheSessionManager:
         if kv_layers:
             eng.model().finish_pending_restore()
             seq = eng.state_manager.get_sequence(uid)
-            kv = eng.state_manager.kv_cache.offload_layers(seq.all_block_ids, kv_layers)
+            kv = eng.state_manager.kv_cache.offload_layers(seq.all_block_ids, kv_layers, layer_major=True)
         kinds = ["none"] * spec.n_layers
         for l in hidden_layers:
             kinds[l] = "hidden"
         for l in kv_layers:
             kinds[l] = "kv"
-        st = SessionState(tokens=tokens, kinds=kinds, hidden=hidden, kv=kv, meta={"turns": len(self._live_tokens[uid])})
+        st = SessionState(tokens=tokens, kinds=kinds, hidden=hidden, kv=kv, meta={"turns": len(self._live_tokens[uid])},
+                          kv_layer_major=True)
         self.store.save(uid, st)
         if not keep_resident:
             eng.flush(uid)

@@ -33,6 +33,7 @@ class SessionState:
     hidden: Optional[torch.Tensor] = None      # [n_hidden_layers, n_tokens, hidden] pinned
     kv: Optional[torch.Tensor] = None          # [n_blocks, n_kv_layers, 2, kv_heads, block_size, head_dim] pinned
     meta: Dict = field(default_factory=dict)
+    kv_layer_major: bool = False               # kv is [n_kv_layers, n_blocks, ...]: one contiguous transfer per layer
 
     @property
     def n_tokens(self) -> int:
@@ -105,7 +106,7 @@ class HiddenStateStore:
     def _write(self, uid: int, st: SessionState) -> None:
         dtype = (st.hidden if st.hidden is not None else st.kv).dtype
         hid = st.hidden.shape[2] if st.hidden is not None else 0
-        kv_shape = [st.kv.shape[0]] + list(st.kv.shape[2:]) if st.kv is not None else None
+        kv_shape = [st.kv.shape[1 if st.kv_layer_major else 0]] + list(st.kv.shape[2:]) if st.kv is not None else None
         tok = st.tokens.to(torch.int32).contiguous()
         hdr = plan_layout(dtype, st.n_tokens, hid, st.kinds, kv_shape,
                           kv_heads=st.kv.shape[3] if st.kv is not None else 0,
@@ -123,7 +124,8 @@ class HiddenStateStore:
                 reqs.append(self._aio.async_pwrite(st.hidden[hi].contiguous(), path, seg.offset))
                 hi += 1
             elif seg.kind == "kv":
-                reqs.append(self._aio.async_pwrite(st.kv[:, ki].contiguous(), path, seg.offset))
+                reqs.append(self._aio.async_pwrite(st.kv[ki] if st.kv_layer_major else st.kv[:, ki].contiguous(), path,
+                                                   seg.offset))
                 ki += 1
         reqs.append(self._aio.async_pwrite(tok, path, hdr.tokens_offset))
         for r in reqs:
@@ -176,10 +178,12 @@ class HiddenStateStore:
         hdr, hidden, kv_layers, tokens, reqs = pending
         for r in reqs:
             self._aio.wait(r)
-        kv = torch.stack(kv_layers, dim=1) if kv_layers else None
+        # segments are stored one layer at a time: come back layer-major, the layout the pipelined reload streams
+        kv = torch.stack(kv_layers, dim=0) if kv_layers else None
         if kv is not None and torch.cuda.is_available():
             kv = kv.pin_memory()
-        st = SessionState(tokens=tokens, kinds=[s.kind for s in hdr.layers], hidden=hidden, kv=kv, meta=dict(hdr.extra))
+        st = SessionState(tokens=tokens, kinds=[s.kind for s in hdr.layers], hidden=hidden, kv=kv, meta=dict(hdr.extra),
+                          kv_layer_major=True)
         with self._lock:
             self.stats["nvme_loads"] += 1
             self.stats["bytes_loaded"] += hdr.payload_bytes

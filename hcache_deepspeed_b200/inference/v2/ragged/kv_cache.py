@@ -126,13 +126,14 @@ class BlockedKVCache:
         host_out.copy_(staging, non_blocking=True)
         return host_out
 
-    def offload_layers(self, blocks: Iterable[int], layers) -> torch.Tensor:
-        """Pages of selected layers only: pinned ``[n_blocks, len(layers), 2, heads, block_size, head_dim]`` (the KV
-        half of a mixed HCache plan; cold path — runs once at the end of a turn)."""
+    def offload_layers(self, blocks: Iterable[int], layers, layer_major: bool = False) -> torch.Tensor:
+        """Pages of selected layers only: pinned ``[n_blocks, len(layers), 2, heads, block_size, head_dim]``, or with
+        ``layer_major`` ``[len(layers), n_blocks, ...]`` (every layer contiguous: the layout the layer-pipelined reload
+        streams). The KV half of a mixed HCache plan; cold path — runs once at the end of a turn."""
         ids = torch.as_tensor(list(blocks) if not isinstance(blocks, torch.Tensor) else blocks, dtype=torch.long)
         lay = torch.as_tensor(list(layers), dtype=torch.long)
         sel = self._cache[lay.to(self._device)][:, ids.to(self._device)]          # [n_l, n_b, 2, h, bs, d]
-        sel = sel.permute(1, 0, 2, 3, 4, 5).contiguous()
+        sel = sel.contiguous() if layer_major else sel.permute(1, 0, 2, 3, 4, 5).contiguous()
         host = pinned_empty(tuple(sel.shape), self._dtype)
         host.copy_(sel)
         return host
