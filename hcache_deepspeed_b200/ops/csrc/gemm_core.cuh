@@ -134,10 +134,7 @@ __device__ __forceinline__ void store_chunk(const GemmArgs& a, int row, int n, f
         for (int j = 0; j < 32; ++j)
             if (n + j < a.N) v[j] += load_scalar<kBf16>(a.bias, n + j);
     }
-    if (a.act != ACT_IDENTITY) {
-#pragma unroll
-        for (int j = 0; j < 32; ++j) v[j] = apply_act(v[j], a.act);
-    }
+    apply_act_vec<32>(v, a.act);
     const int64_t off = static_cast<int64_t>(row) * a.ldo + n;
     char* dst = reinterpret_cast<char*>(a.out) + off * 2;
     if (n + 32 <= a.N && (reinterpret_cast<uintptr_t>(dst) & 15) == 0) {
@@ -150,17 +147,19 @@ __device__ __forceinline__ void store_chunk(const GemmArgs& a, int row, int n, f
 // GATED epilogue: N counts interleaved (gate, up) columns; the output has N/2 columns.
 template <bool kBf16>
 __device__ __forceinline__ void gated_chunk(const GemmArgs& a, int row, int n, float (&v)[32]) {
-    float o[16];
+    float o[16], u[16];
 #pragma unroll
     for (int j = 0; j < 16; ++j) {
-        float g = v[2 * j];
-        float u = v[2 * j + 1];
+        o[j] = v[2 * j];
+        u[j] = v[2 * j + 1];
         if (a.bias != nullptr && n + 2 * j + 1 < a.N) {
-            g += load_scalar<kBf16>(a.bias, n + 2 * j);
-            u += load_scalar<kBf16>(a.bias, n + 2 * j + 1);
+            o[j] += load_scalar<kBf16>(a.bias, n + 2 * j);
+            u[j] += load_scalar<kBf16>(a.bias, n + 2 * j + 1);
         }
-        o[j] = apply_act(g, a.act) * u;
     }
+    apply_act_vec<16>(o, a.act);
+#pragma unroll
+    for (int j = 0; j < 16; ++j) o[j] *= u[j];
     const int64_t off = static_cast<int64_t>(row) * a.ldo + (n >> 1);
     char* dst = reinterpret_cast<char*>(a.out) + off * 2;
     if (n + 32 <= a.N && (reinterpret_cast<uintptr_t>(dst) & 15) == 0) {

@@ -71,24 +71,23 @@ template <int NT, bool kBf16, bool kGated>
 __device__ __forceinline__ void skinny_finalize(const SkinnyArgs& a, int n, uint32_t lane, float (&v)[NT]) {
     const bool live = n < a.N;
     const float b = (a.bias != nullptr && live) ? load_scalar<kBf16>(a.bias, n) : 0.0f;
+#pragma unroll
+    for (int t = 0; t < NT; ++t) v[t] += b;
     if constexpr (kGated) {
+        // even lanes hold gate features (activated), odd lanes the matching up features (left as they are)
+        apply_act_vec<NT>(v, (lane & 1) ? static_cast<int>(ACT_IDENTITY) : a.act);
 #pragma unroll
         for (int t = 0; t < NT; ++t) {
-            const float x = v[t] + b;
-            const float partner = __shfl_xor_sync(0xffffffffu, x, 1);
+            const float partner = __shfl_xor_sync(0xffffffffu, v[t], 1);
             if (live && !(lane & 1) && t < a.M)
-                store_scalar<kBf16>(a.out, static_cast<int64_t>(t) * a.ldo + (n >> 1), apply_act(x, a.act) * partner);
+                store_scalar<kBf16>(a.out, static_cast<int64_t>(t) * a.ldo + (n >> 1), v[t] * partner);
         }
     } else {
         if (!live) return;
+        apply_act_vec<NT>(v, a.act);
 #pragma unroll
-        for (int t = 0; t < NT; ++t) {
-            if (t < a.M) {
-                float x = v[t] + b;
-                if (a.act != ACT_IDENTITY) x = apply_act(x, a.act);
-                store_scalar<kBf16>(a.out, static_cast<int64_t>(t) * a.ldo + n, x);
-            }
-        }
+        for (int t = 0; t < NT; ++t)
+            if (t < a.M) store_scalar<kBf16>(a.out, static_cast<int64_t>(t) * a.ldo + n, v[t]);
     }
 }
 

@@ -58,6 +58,11 @@ elif case == "gemm_2sm":
     a, w = rand(M, Kd), rand(N, Kd, scale=Kd ** -0.5)
     out = torch.empty(M, N, device=dev, dtype=torch.bfloat16)
     fn = lambda: K.gemm_2sm(a, w, out=out, bn=256)
+elif case == "gemm_2sm_silu":
+    M, N, Kd = 4160, 22016, 4096
+    a, w = rand(M, Kd), rand(N, Kd, scale=Kd ** -0.5)
+    out = torch.empty(M, N, device=dev, dtype=torch.bfloat16)
+    fn = lambda: K.gemm_2sm(a, w, out=out, act=3, bn=256)
 elif case == "gemm_fp8":
     M, N, Kd = 4096, 12288, 4096
     a, w = rand(M, Kd), rand(N, Kd, scale=Kd ** -0.5)
