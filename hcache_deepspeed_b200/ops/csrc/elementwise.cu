@@ -237,7 +237,7 @@ __global__ void rope_kv_append_kernel(const void* __restrict__ qkv, int64_t ld_q
 #pragma unroll
         for (int j = 0; j < 8; ++j) {
             float s, c;
-            sincosf(pos * inv_freq[f0 + j], &s, &c);
+            rope_sincos(pos * inv_freq[f0 + j], &s, &c);
             x[j] = low ? (x[j] * c - y[j] * s) : (x[j] * c + y[j] * s);
         }
     }

@@ -360,7 +360,7 @@ __device__ __forceinline__ void epilogue_kv_rope(const GemmArgs& a, uint32_t tad
 #pragma unroll 4
                     for (int j = 0; j < 32; ++j) {
                         float sn, co;
-                        sincosf(static_cast<float>(pos) * a.inv_freq[c + j], &sn, &co);
+                        rope_sincos(static_cast<float>(pos) * a.inv_freq[c + j], &sn, &co);
                         const float x = lo[j], y = hi[j];
                         lo[j] = x * co - y * sn;
                         hi[j] = y * co + x * sn;

@@ -380,6 +380,17 @@ __device__ __forceinline__ float warp_max(float v) {
 
 enum Activation : int { ACT_IDENTITY = 0, ACT_GELU = 1, ACT_RELU = 2, ACT_SILU = 3, ACT_GELU_TANH = 4 };
 
+// sin / cos of a RoPE angle (position x inverse frequency: up to ~1e5 rad). Two-constant Cody-Waite reduction to
+// [-pi, pi] followed by the SFU approximations: absolute error ~1e-6, far below the 6e-8 * |x| the fp32 product
+// pos * inv_freq already carries. The library sincosf takes a branchy slow path for large arguments (stack frame,
+// divergence) and made the RoPE kernels compute-bound: rope_kv_append ran 13x over its memory time.
+__device__ __forceinline__ void rope_sincos(float x, float* s, float* c) {
+    const float k = rintf(x * 0.15915494309189535f);
+    float r = fmaf(-k, 6.28318548202514648f, x);
+    r = fmaf(-k, -1.74845553e-7f, r);
+    __sincosf(r, s, c);
+}
+
 // Activations are applied inside unrolled epilogue loops (16-64 copies per kernel), so the body must stay small: the
 // erf form of GELU is an out-of-line call, everything else is a handful of instructions on the fast-math intrinsics
 // (an inlined switch over erff / tanhf made the epilogues instruction-fetch bound: a 4160 x 22016 store epilogue took
