@@ -196,12 +196,13 @@ def make_slots(T, n_blocks, bs, seed=0):
     return perm.to(torch.int32).cuda()
 
 
+@pytest.mark.parametrize("max_pos", [5000, 200000])     # long contexts: the in-kernel range reduction must hold up
 @pytest.mark.parametrize("d,rd,n_q,n_kv", [(128, 128, 4, 4), (128, 128, 8, 2), (64, 64, 12, 12), (80, 32, 4, 4), (96, 96, 2, 1)])
-def test_rope_kv_append(d, rd, n_q, n_kv):
+def test_rope_kv_append(d, rd, n_q, n_kv, max_pos):
     torch.manual_seed(7)
     T, bs, n_blocks = 45, 64, 6
     qkv = rand(T, (n_q + 2 * n_kv) * d)
-    pos = torch.randint(0, 5000, (T,), device="cuda", dtype=torch.int32)
+    pos = torch.randint(max_pos // 2, max_pos, (T,), device="cuda", dtype=torch.int32)
     slot = make_slots(T, n_blocks, bs)
     slot[3] = -1
     inv = ref.default_inv_freq(rd, device="cuda")
