@@ -204,7 +204,8 @@ static int launch_norm_vpt(int rows, int cols, const void* x, void* delta, void*
 
 // ---------------------------------------------------------------------------------------------
 // RoPE + paged KV append (unfused path: arbitrary head_dim % 8 == 0, partial rotary dims)
-// grid (tokens, n_q + 2*n_kv heads); each thread owns one 8-element vector of one head.
+// grid (tokens, ceil(vectors per token / 256)); each thread owns one 8-element vector of one head (full warps: with one
+// 16-lane block per (token, head) a 4160-token prefill launched 400k blocks and ran 13x over its memory time).
 // ---------------------------------------------------------------------------------------------
 template <bool kBf16>
 __global__ void rope_kv_append_kernel(const void* __restrict__ qkv, int64_t ld_qkv, void* __restrict__ q_out,
@@ -213,9 +214,11 @@ __global__ void rope_kv_append_kernel(const void* __restrict__ qkv, int64_t ld_q
                                       int n_q, int n_kv, int d, int rotary_dim, int block_size, int do_rope) {
     pdl_enter();
     const int t = blockIdx.x;
-    const int head = blockIdx.y;
-    const int vi = threadIdx.x;
-    if (vi * 8 >= d) return;
+    const int vec_per_head = d >> 3;
+    const int idx = blockIdx.y * blockDim.x + threadIdx.x;   // vector index over all heads of this token
+    const int head = idx / vec_per_head;
+    const int vi = idx - head * vec_per_head;
+    if (head >= n_q + 2 * n_kv) return;
     const bool is_q = head < n_q;
     const bool is_k = !is_q && head < n_q + n_kv;
     const int slot = tok_slot[t];
@@ -476,8 +479,9 @@ extern "C" int hds_rope_kv_append(const void* qkv, int64_t ld_qkv, void* q_out, 
                 "hds_rope_kv_append: rotary_dim must be a multiple of 16 and <= head_dim");
     HDS_REQUIRE(ld_qkv % 8 == 0, "hds_rope_kv_append: ld_qkv must be a multiple of 8");
     if (T == 0) return HDS_OK;
-    dim3 grid(T, n_q_heads + 2 * n_kv_heads);
-    const int threads = ((head_dim / 8 + 31) / 32) * 32;
+    const int vectors = (n_q_heads + 2 * n_kv_heads) * (head_dim / 8);
+    const int threads = vectors < 256 ? ((vectors + 31) / 32) * 32 : 256;
+    dim3 grid(T, (vectors + threads - 1) / threads);
     cudaStream_t s = static_cast<cudaStream_t>(stream);
     if (dtype == 0)
         launch_kernel(rope_kv_append_kernel<true>, grid, dim3(threads), 0, s, qkv, ld_qkv, q_out, kv_cache_layer, tok_pos, tok_slot,
