@@ -45,7 +45,7 @@ def parse():
     p.add_argument("--quant", default="none", choices=["none", "wf8af8"],
                    help="none (default, the bf16 headline configuration) or wf8af8: E4M3 weights + per-token fp8 activations; "
                         "reported with dtype fp8-w8a8 and NOT comparable with the bf16 baseline")
-    p.add_argument("--plan", default="hidden", choices=["auto", "hidden", "planner"],
+    p.add_argument("--plan", default="hidden", choices=["auto", "hidden", "planner", "adaptive"],
                    help="hidden: every layer from hidden states (fastest measured on 1xB200: 20.4 ms vs 21.6 ms); auto: planner mix with a recomputed prefix")
     return p.parse_args()
 
@@ -146,9 +146,32 @@ def run_ours(a):
     torch.cuda.synchronize()
     eng.flush(10 ** 9)
     prefill_s = p0.elapsed_time(p1) / 1e3
+    # adaptive: measure the host link as it is DURING the run (every rank copies at once, as in the timed region); when
+    # the ranks contend for host memory bandwidth the planner trades transfers for a recomputed prefix of layers
+    link = LinkModel(tp_size=tp)
+    allow_recompute = a.plan == "auto"
+    if a.plan == "adaptive" and tp == 1:
+        probe_src = latents[:4]
+        probe_dst = torch.empty(probe_src.shape, dtype=probe_src.dtype, device=dev)
+        probe_dst.copy_(probe_src, non_blocking=True)
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+        c0, c1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        c0.record()
+        for _ in range(4):
+            probe_dst.copy_(probe_src, non_blocking=True)
+        c1.record()
+        torch.cuda.synchronize()
+        bw = torch.tensor([4 * probe_src.numel() * 2 / (c0.elapsed_time(c1) / 1e3)], device=dev)
+        if world > 1:
+            dist.all_reduce(bw, op=dist.ReduceOp.MIN)
+        link = LinkModel(tp_size=tp, io_bytes_per_s=float(bw.item()))
+        allow_recompute = link.io_bytes_per_s < 0.8 * LinkModel().io_bytes_per_s     # only when the link is contended
+        del probe_dst
     # planner: hidden states vs offloaded KV pages per layer by bytes moved (GQA models: KV is smaller than the hidden state)
-    plan = plan_restore(spec, ctx, LinkModel(tp_size=tp), allow_kv=(a.plan == "planner" and tp == 1),
-                        allow_recompute=(a.plan == "auto"), extra_compute_s=prefill_s)
+    plan = plan_restore(spec, ctx, link, allow_kv=(a.plan == "planner" and tp == 1),
+                        allow_recompute=allow_recompute, extra_compute_s=prefill_s)
     hidden_layers, recompute_layers, kv_layers = plan.layers_of("hidden"), plan.layers_of("none"), plan.layers_of("kv")
     lat_hidden = latents[hidden_layers[0]:hidden_layers[-1] + 1] if hidden_layers else None  # a contiguous run of layers
     kv_pages = None
@@ -257,6 +280,7 @@ def run_ours(a):
                        "restore_plan": {"recompute_prefix_layers": 0 if sharded else len(recompute_layers),
                                         "hidden_state_layers": spec.n_layers if sharded else len(hidden_layers),
                                         "kv_offload_layers": 0 if sharded else len(kv_layers), "tp_sharded_restore": sharded,
+                                        "host_link_GBps": round(link.io_bytes_per_s / 1e9, 1),
                                         "tp_collectives": "fused GEMM-epilogue reduction" if bool(getattr(model.comm, "fused", False))
                                         else ("nccl" if tp > 1 else "none")},
                        "l2_policy": f"working set per step (weights {model.w.n_bytes() / 2**30:.1f} GiB + KV) exceeds the 126 MB L2"},
