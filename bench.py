@@ -151,24 +151,9 @@ def run_ours(a):
     link = LinkModel(tp_size=tp)
     allow_recompute = a.plan == "auto"
     if a.plan == "adaptive" and tp == 1:
-        probe_src = latents[:4]
-        probe_dst = torch.empty(probe_src.shape, dtype=probe_src.dtype, device=dev)
-        probe_dst.copy_(probe_src, non_blocking=True)
-        torch.cuda.synchronize()
-        if world > 1:
-            dist.barrier()
-        c0, c1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        c0.record()
-        for _ in range(4):
-            probe_dst.copy_(probe_src, non_blocking=True)
-        c1.record()
-        torch.cuda.synchronize()
-        bw = torch.tensor([4 * probe_src.numel() * 2 / (c0.elapsed_time(c1) / 1e3)], device=dev)
-        if world > 1:
-            dist.all_reduce(bw, op=dist.ReduceOp.MIN)
-        link = LinkModel(tp_size=tp, io_bytes_per_s=float(bw.item()))
+        from hcache_deepspeed_b200.hcache import measure_link
+        link = measure_link(dev, tp_size=tp)
         allow_recompute = link.io_bytes_per_s < 0.8 * LinkModel().io_bytes_per_s     # only when the link is contended
-        del probe_dst
     # planner: hidden states vs offloaded KV pages per layer by bytes moved (GQA models: KV is smaller than the hidden state)
     plan = plan_restore(spec, ctx, link, allow_kv=(a.plan == "planner" and tp == 1),
                         allow_recompute=allow_recompute, extra_compute_s=prefill_s)

@@ -103,3 +103,31 @@ def plan_restore(spec: ArchSpec, n_tokens: int, link: Optional[LinkModel] = None
 def storage_bytes(spec: ArchSpec, n_tokens: int, plan: RestorePlan, elem: int = 2) -> int:
     per = {"hidden": spec.hidden * elem, "kv": 2 * spec.kv_dim * elem, "none": 0}
     return sum(per[k] for k in plan.kinds) * n_tokens
+
+
+def measure_link(device, nbytes: int = 128 << 20, repeats: int = 4, group=None, tp_size: int = 1) -> LinkModel:
+    """A :class:`LinkModel` whose host-to-device rate is MEASURED: every rank of ``group`` (default: all ranks) copies a
+    pinned buffer at the same time, as restores do in steady state, and the slowest rank's rate is taken. On a node
+    whose GPUs share host memory bandwidth the contended rate can be less than half of the single-GPU one, which moves
+    the planner's optimum from "transfer everything" to "recompute a prefix" (``profiles/bench_runs.md``)."""
+    import torch
+    if getattr(device, "type", str(device)) != "cuda" or not torch.cuda.is_available():
+        return LinkModel(tp_size=tp_size)
+    import torch.distributed as dist
+    src = torch.empty(nbytes, dtype=torch.uint8, pin_memory=True)
+    dst = torch.empty(nbytes, dtype=torch.uint8, device=device)
+    dst.copy_(src, non_blocking=True)
+    torch.cuda.synchronize(device)
+    multi = dist.is_available() and dist.is_initialized() and dist.get_world_size(group) > 1
+    if multi:
+        dist.barrier(group=group)
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(repeats):
+        dst.copy_(src, non_blocking=True)
+    e1.record()
+    torch.cuda.synchronize(device)
+    bw = torch.tensor([repeats * nbytes / (e0.elapsed_time(e1) / 1e3)], device=device)
+    if multi:
+        dist.all_reduce(bw, op=dist.ReduceOp.MIN, group=group)
+    return LinkModel(io_bytes_per_s=float(bw.item()), tp_size=tp_size)

@@ -12,16 +12,20 @@ from typing import Callable, Dict, List, Optional
 import torch
 
 from ..inference.sampling import sample_next
-from .planner import LinkModel, RestorePlan, plan_restore
+from .planner import LinkModel, RestorePlan, measure_link, plan_restore
 from .store import HiddenStateStore, SessionState
 
 
 class HCacheSessionManager:
 
     def __init__(self, engine, store: Optional[HiddenStateStore] = None, link: Optional[LinkModel] = None,
-                 allow_recompute: bool = True, allow_kv: bool = True) -> None:
+                 allow_recompute: bool = True, allow_kv: bool = True, measure_host_link: bool = False) -> None:
+        """``measure_host_link``: calibrate the planner with the host link as it is when every rank transfers at once
+        (collective over the default process group when one is initialised) instead of the built-in single-GPU rate."""
         self.engine = engine
         self.store = store or HiddenStateStore()
+        if link is None and measure_host_link:
+            link = measure_link(engine.model().device, tp_size=engine.model().tp_size)
         self.link = link or LinkModel(tp_size=engine.model().tp_size)
         self.allow_recompute, self.allow_kv = allow_recompute, allow_kv
         self._live_latents: Dict[int, List[torch.Tensor]] = {}
