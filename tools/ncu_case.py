@@ -63,6 +63,21 @@ elif case == "gemm_2sm_silu":
     a, w = rand(M, Kd), rand(N, Kd, scale=Kd ** -0.5)
     out = torch.empty(M, N, device=dev, dtype=torch.bfloat16)
     fn = lambda: K.gemm_2sm(a, w, out=out, act=3, bn=256)
+elif case == "gemm_fp8_2sm_gated":
+    M, N, Kd = 4160, 22016, 4096
+    a, w = rand(M, Kd), rand(N, Kd, scale=Kd ** -0.5)
+    aq, a_s = K.quantize_fp8_rows(a)
+    wq, w_s = K.quantize_fp8_rows(w)
+    out = torch.empty(M, N // 2, device=dev, dtype=torch.bfloat16)
+    fn = lambda: K.gemm_fp8(aq, a_s, wq, w_s, out, act=3, gated=True, bn=1256)
+elif case == "decode_gated_fp8":
+    M, N, Kd = 8, 22016, 4096
+    a, w = rand(M, Kd), rand(N, Kd, scale=Kd ** -0.5)
+    aq, a_s = K.quantize_fp8_rows(a)
+    wq, w_s = K.quantize_fp8_rows(w)
+    out = torch.empty(M, N // 2, device=dev, dtype=torch.bfloat16)
+    ws = torch.zeros(K.gemm_fp8_skinny_workspace_bytes(M, N), dtype=torch.uint8, device=dev)
+    fn = lambda: K.gemm_fp8(aq, a_s, wq, w_s, out, act=3, gated=True, workspace=ws)
 elif case == "gemm_fp8":
     M, N, Kd = 4096, 12288, 4096
     a, w = rand(M, Kd), rand(N, Kd, scale=Kd ** -0.5)
