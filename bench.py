@@ -42,6 +42,10 @@ def parse():
                    help="N > 1: 'dp' = one full replica per GPU serving its own sessions (a 7B model fits 13x in 180 GB; "
                         "what a deployment does for throughput), 'tp' = one engine tensor-parallel over all GPUs (fused "
                         "NVLink collectives, PCIe-sharded restore: lower TTFT, lower aggregate throughput)")
+    p.add_argument("--source", default="dram", choices=["dram", "nvme"],
+                   help="where a session's hidden states live before the restore: pinned host DRAM (headline) or a file read "
+                        "back through the O_DIRECT aio engine inside the timed region (NVMe tier)")
+    p.add_argument("--nvme-dir", default="/tmp/hds_bench_nvme")
     p.add_argument("--quant", default="none", choices=["none", "wf8af8"],
                    help="none (default, the bf16 headline configuration) or wf8af8: E4M3 weights + per-token fp8 activations; "
                         "reported with dtype fp8-w8a8 and NOT comparable with the bf16 baseline")
@@ -167,6 +171,17 @@ def run_ours(a):
                                pin_memory=True)
         kv_pages.copy_((torch.randn(kv_pages.shape, generator=g) * 0.3).to(torch.bfloat16))
     interleave = plan.interleave
+    nvme = None
+    if a.source == "nvme" and tp == 1 and lat_hidden is not None:
+        # NVMe tier: the session's hidden states sit in a file; every restore reads them back (one request per layer, all
+        # aio threads in flight, O_DIRECT so the page cache cannot serve them) into the pinned staging tensor first
+        from hcache_deepspeed_b200.io.aio import AsyncIOHandle
+        os.makedirs(a.nvme_dir, exist_ok=True)
+        nvme = {"h": AsyncIOHandle(block_size=8 << 20, queue_depth=32, intra_op_parallelism=8, use_direct=True),
+                "path": os.path.join(a.nvme_dir, f"hds_bench_rank{rank}.bin"),
+                "layer_bytes": lat_hidden[0].numel() * 2}
+        for l in range(lat_hidden.shape[0]):
+            nvme["h"].sync_pwrite(lat_hidden[l], nvme["path"], l * nvme["layer_bytes"])
     # tensor parallel: every rank keeps (and transfers) only its 1/tp row slice of the hidden states; the restore
     # kernels gather the slices from peer HBM over NVLink (needs the fused/symmetric-memory communicator)
     sharded = tp > 1 and bool(getattr(model.comm, "fused", False))
@@ -188,6 +203,11 @@ def run_ours(a):
         for i, uid in enumerate(uids):
             t0, e0, e1 = time.perf_counter(), ev(), ev()
             e0.record()
+            if nvme is not None:
+                reqs = [nvme["h"].async_pread(lat_hidden[l], nvme["path"], l * nvme["layer_bytes"])
+                        for l in range(lat_hidden.shape[0])]
+                for r_ in reqs:
+                    nvme["h"].wait(r_)
             if sharded:
                 eng.restore_kv([uid], [ctx_tokens], [lat_slice], do_checks=False, sharded=True)
             else:
@@ -237,6 +257,11 @@ def run_ours(a):
         dist.barrier()
     torch.cuda.synchronize()
     clocks = sampler.stop() if rank == 0 else None
+    if nvme is not None:
+        try:
+            os.remove(nvme["path"])
+        except OSError:
+            pass
     total_ms = s_all.elapsed_time(e_all)
     stats = torch.tensor([total_ms, sum(rec["decode_dev_ms"]), sum(rec["decode_host_ms"]),
                           statistics.median(rec["ttft_dev_ms"]), statistics.median(rec["ttft_host_ms"])], device=dev)
@@ -261,7 +286,7 @@ def run_ours(a):
             "config": {"model": a.model, "global_batch": B * replicas, "seq_len": ctx + n_new + D,
                        "parallelism": f"tp{tp}" if replicas == 1 else f"dp{replicas}",
                        "restored_ctx": ctx, "new_turn_tokens": n_new, "decode_steps": D, "sessions_per_gpu": a.sessions,
-                       "numa_bound_cpus": len(numa_cpus),
+                       "numa_bound_cpus": len(numa_cpus), "hidden_state_source": a.source if nvme is not None or a.source == "dram" else "dram",
                        "restore_plan": {"recompute_prefix_layers": 0 if sharded else len(recompute_layers),
                                         "hidden_state_layers": spec.n_layers if sharded else len(hidden_layers),
                                         "kv_offload_layers": 0 if sharded else len(kv_layers), "tp_sharded_restore": sharded,
