@@ -1,0 +1,103 @@
+"""ZeRO support modules: contiguous allocator with compaction, memory-lean linear, offload-state helpers, utils."""
+from collections import namedtuple
+
+import pytest
+import torch
+
+from hcache_deepspeed_b200.runtime.zero.contiguous_memory_allocator import ContiguousMemoryAllocator
+from hcache_deepspeed_b200.runtime.zero.linear import LinearModuleForZeroStage3, zero3_linear_wrap
+from hcache_deepspeed_b200.runtime.zero.offload_states import (OffloadStateTypeEnum, get_state_devices, offload_adam_states,
+                                                              reload_adam_states)
+from hcache_deepspeed_b200.runtime.zero.partitioned_param_profiler import PartitionedParameterProfiler
+from hcache_deepspeed_b200.runtime.zero.utils import (apply_to_tensors_only, assert_ints_same_as_other_ranks,
+                                                     get_mapping_to_flat_buffer, is_zero_supported_optimizer,
+                                                     isinstance_namedtuple)
+
+
+def test_contiguous_allocator_defragments_and_keeps_handles():
+    mem = ContiguousMemoryAllocator(1024, torch.float32, "cpu")
+    a = mem.allocate_tensor(64)
+    b = mem.allocate_tensor(64)
+    c = mem.allocate_tensor(128)
+    d = mem.allocate_tensor(256)
+    e = mem.allocate_tensor(512)
+    assert mem.total_free == 0 and mem.max_allocated == 1024
+    for i, t in enumerate((a, b, c, d, e)):
+        t.fill_(float(i + 1))
+    p = torch.nn.Parameter(torch.empty(0))
+    mem.assign_to_param(d, p, 200, (10, 20))
+    assert p.shape == (10, 20) and float(p.sum()) == 4.0 * 200
+    mem.release_tensor(a)
+    mem.release_tensor(c)
+    assert mem.total_free == 192 and mem.largest_contiguous == 128
+    assert mem.contiguous_sizes == {0: 64, 128: 128}
+    # 192 free in total but not in one piece: compaction has to move b, d and e
+    f = mem.allocate_tensor(192)
+    f.fill_(9.0)
+    assert mem.total_free == 0
+    assert torch.all(b == 2.0) and torch.all(d == 4.0) and torch.all(e == 5.0)
+    assert float(p.sum()) == 4.0 * 200
+    assert p.data_ptr() == d.data_ptr() and b.data_ptr() == mem.buffer.data_ptr()
+    # writes through the handle still land in the parameter after the move
+    d.fill_(7.0)
+    assert float(p.sum()) == 7.0 * 200
+    with pytest.raises(AssertionError):
+        mem.allocate_tensor(1)
+    mem.release_tensor(e)
+    assert mem.largest_contiguous == 512 and "x" in mem.print_allocation(32)
+
+
+def test_zero3_linear_matches_nn_linear():
+    torch.manual_seed(0)
+    ref = torch.nn.Linear(24, 12)
+    mod = LinearModuleForZeroStage3(24, 12)
+    mod.load_state_dict(ref.state_dict())
+    x1 = torch.randn(3, 5, 24, requires_grad=True)
+    x2 = x1.detach().clone().requires_grad_(True)
+    ref(x1).square().sum().backward()
+    mod(x2).square().sum().backward()
+    assert torch.allclose(x1.grad, x2.grad, atol=1e-5)
+    assert torch.allclose(ref.weight.grad, mod.weight.grad, atol=1e-4)
+    assert torch.allclose(ref.bias.grad, mod.bias.grad, atol=1e-4)
+    y = zero3_linear_wrap(x1.detach(), ref.weight.detach())
+    assert torch.allclose(y, x1.detach() @ ref.weight.detach().t())
+
+
+def test_offload_and_reload_adam_states():
+    lin = torch.nn.Linear(8, 8)
+    opt = torch.optim.Adam(lin.parameters(), lr=1e-2)
+    lin(torch.randn(4, 8)).sum().backward()
+    opt.step()
+    before = {id(p): opt.state[p]["exp_avg"].clone() for p in lin.parameters()}
+    offload_adam_states(opt, "cpu")
+    assert get_state_devices(opt, OffloadStateTypeEnum.optim_states) == {torch.device("cpu")}
+    reload_adam_states(opt, "cpu")
+    for p in lin.parameters():
+        assert torch.equal(opt.state[p]["exp_avg"], before[id(p)])
+    opt.zero_grad()
+    lin(torch.randn(4, 8)).sum().backward()
+    opt.step()       # the states are still usable
+
+
+def test_zero_utils_tree_map_and_flat_map():
+    Pair = namedtuple("Pair", "a b")
+    tree = {"x": [torch.ones(2), 3], "y": Pair(torch.zeros(1), "s")}
+    out = apply_to_tensors_only(lambda t: t + 1, tree)
+    assert torch.equal(out["x"][0], torch.full((2,), 2.0)) and out["x"][1] == 3
+    assert isinstance_namedtuple(out["y"]) and float(out["y"].a) == 1.0 and out["y"].b == "s"
+    m = get_mapping_to_flat_buffer([torch.empty(3), torch.empty(2, 2)])
+    assert [(o, n) for _, o, n in m] == [(0, 3), (3, 4)]
+    assert is_zero_supported_optimizer(torch.optim.AdamW([torch.nn.Parameter(torch.ones(1))]))
+    assert not is_zero_supported_optimizer(object())
+    assert_ints_same_as_other_ranks([1, 2, 3])      # single process: a no-op
+
+
+def test_partitioned_param_profiler_counts():
+    prof = PartitionedParameterProfiler()
+    for n in (10, 20):
+        prof.start_event("fetch")
+        prof.stop_event("fetch", n)
+    c = prof.event_counters["fetch"]
+    assert (c.count, c.num_elem) == (2, 30) and prof.elapsed["fetch"] >= 0
+    prof.reset_events()
+    assert prof.event_counters["fetch"].count == 0
