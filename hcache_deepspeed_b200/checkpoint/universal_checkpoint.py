@@ -16,14 +16,13 @@ def load_hp_checkpoint_state(folder: str, name: str, key: str = "fp32") -> Optio
     return obj["param"] if isinstance(obj, dict) else obj
 
 
-def load_universal_into_engine(engine, folder: str, load_optimizer_states: bool = True) -> int:
-    """Fill the module's parameters, and — for ZeRO-1/2 / BF16 optimizers — this rank's fp32 master slices and Adam
-    moments, from a universal checkpoint. Returns the number of parameters restored."""
-    from ..runtime.zero.stage_1_and_2 import DeepSpeedZeroOptimizer
+def load_universal_into_optimizer(opt, folder: str, load_optimizer_states: bool = True,
+                                  lp_groups_name: str = "bit16_groups") -> int:
+    """This rank's fp32 master slices and Adam moments of a ZeRO-1/2 / BF16 optimizer, cut out of the per-parameter
+    files (``base_optimizer.py:20-63`` of the reference does this per lp parameter)."""
     restored = 0
-    opt = engine.optimizer
-    if isinstance(opt, DeepSpeedZeroOptimizer):
-        for gi, params in enumerate(opt.bit16_groups):
+    if True:
+        for gi, params in enumerate(getattr(opt, lp_groups_name)):
             if not params:
                 continue
             flat = opt.bit16_groups_flat[gi]
@@ -57,7 +56,17 @@ def load_universal_into_engine(engine, folder: str, load_optimizer_states: bool 
             if opt.partition_count > 1:
                 from .. import comm as dist
                 dist.all_gather_into_tensor(flat, flat.narrow(0, lo, psize).clone(), group=opt.dp_process_group)
-        return restored
+    return restored
+
+
+def load_universal_into_engine(engine, folder: str, load_optimizer_states: bool = True) -> int:
+    """Fill the module's parameters, and — for ZeRO-1/2 / BF16 optimizers — this rank's fp32 master slices and Adam
+    moments, from a universal checkpoint. Returns the number of parameters restored."""
+    from ..runtime.zero.stage_1_and_2 import DeepSpeedZeroOptimizer
+    restored = 0
+    opt = engine.optimizer
+    if isinstance(opt, DeepSpeedZeroOptimizer):
+        return load_universal_into_optimizer(opt, folder, load_optimizer_states)
     for name, p in engine.module.named_parameters():
         full = load_hp_checkpoint_state(folder, name, "fp32")
         if full is not None:

@@ -101,3 +101,21 @@ def test_partitioned_param_profiler_counts():
     assert (c.count, c.num_elem) == (2, 30) and prof.elapsed["fetch"] >= 0
     prof.reset_events()
     assert prof.event_counters["fetch"].count == 0
+
+
+def test_runtime_name_parity_modules():
+    import json
+
+    from hcache_deepspeed_b200.runtime import base_optimizer, compiler, config_utils, constants
+    from hcache_deepspeed_b200.runtime.bf16_optimizer import BF16_Optimizer
+    from hcache_deepspeed_b200.runtime.zero.stage3 import DeepSpeedZeroOptimizer_Stage3
+    assert issubclass(BF16_Optimizer, base_optimizer.ZeROOptimizer)
+    assert issubclass(DeepSpeedZeroOptimizer_Stage3, base_optimizer.DeepSpeedOptimizer)
+    assert hasattr(BF16_Optimizer, "load_hp_checkpoint_state_from_checkpoint_dir")
+    assert constants.TRAIN_BATCH_SIZE == "train_batch_size" and constants.GRADIENT_CLIPPING_DEFAULT == 0.0
+    assert constants.defaults()["steps_per_print"] == 10
+    text = json.dumps({"bucket": 5e8, "small": 12, "flag": True, "l": [1, 2]}, cls=config_utils.ScientificNotationEncoder)
+    assert "5.000000e+08" in text and '"small": 12' in text and "true" in text
+    assert config_utils.get_scalar_param({"a": 1}, "b", 7) == 7
+    f = compiler.disable(lambda x: x + 1)
+    assert f(1) == 2 and not compiler.is_compiling()
