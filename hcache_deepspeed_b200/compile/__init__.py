@@ -1,15 +1,12 @@
-"""DeepCompile (``deepspeed/compile`` + ``csrc/compile``) is a ``torch.compile`` back end with ZeRO-aware graph passes.
-This framework deliberately has no tracing-compiler path (streams + CUDA graphs instead), so the entry
-points exist and explain that rather than silently doing nothing."""
+"""Schedule compiler — this framework's counterpart of DeepCompile (``deepspeed/compile`` + ``csrc/compile``).
 
-
-def is_deepcompile_supported() -> bool:
-    return False
-
-
-def init_z1(*args, **kwargs):
-    raise NotImplementedError("DeepCompile is not part of the B200-native runtime: use ZeRO stage 1 without compile")
-
-
-def init_z3(*args, **kwargs):
-    raise NotImplementedError("DeepCompile is not part of the B200-native runtime: use ZeRO stage 3 without compile")
+DeepCompile is a ``torch.compile`` back end with ZeRO-aware FX-graph passes. This runtime keeps tracing compilers off
+its path (streams + CUDA graphs instead) and gets the same optimisations — prefetching of parameter
+gathers, selective (persistent) gathering, optimizer-state / activation / parameter offload — by scheduling on the
+MODULE trace that the ZeRO-3 hooks record: see :mod:`.backend`."""
+from .backend import launch_compile_passes, make_backend, opt_passes, register_compile_pass  # noqa: F401
+from .config import CompileConfig  # noqa: F401
+from .init_z1 import init_z1  # noqa: F401
+from .init_z3 import init_z3  # noqa: F401
+from .trace import ModuleTrace, TraceEvent  # noqa: F401
+from .util import is_deepcompile_supported  # noqa: F401

@@ -598,6 +598,44 @@ class DeepSpeedEngine(torch.nn.Module):
                 self.lr_scheduler.step()
         self.global_steps += 1
         self.global_samples += self.train_batch_size()
+        self._maybe_launch_compile_passes()
+
+    # ---- schedule compiler (the reference's engine.compile / DeepCompile, engine.py:3890+) ---------------------------
+    def is_deepcompile_enabled(self) -> bool:
+        return bool((self._config.compile_config or {}).get("deepcompile", False))
+
+    @property
+    def is_compiled(self) -> bool:
+        return getattr(self, "_is_compiled", False)
+
+    def compile(self, backend=None, compile_kwargs=None, schedule=None) -> None:
+        """Arm the schedule compiler: after the next optimizer step (one profiled iteration) the passes run once and
+        their result (prefetch plan, persistent parameters, optimizer-state offload) is applied to this engine.
+        ``backend`` / ``compile_kwargs`` are accepted for signature parity; no tracing compiler is involved."""
+        from ..compile import init_z1, init_z3
+        if self.is_compiled:
+            return
+        if self.zero_optimization_stage() == 3:
+            self._compile_fn = init_z3(self, backend, self._config.compile_config, compile_kwargs, schedule)
+        elif self.zero_optimization_stage() in (1, 2):
+            self._compile_fn = init_z1(self, backend, self._config.compile_config, compile_kwargs, schedule,
+                                       use_z2=self.zero_optimization_stage() == 2)
+        else:
+            raise RuntimeError("engine.compile() schedules ZeRO collectives: it needs zero_optimization.stage >= 1")
+        self._is_compiled = True
+        self.compile_report = None
+
+    def _maybe_launch_compile_passes(self):
+        fn = getattr(self, "_compile_fn", None)
+        if fn is None:
+            return
+        off = getattr(self.optimizer, "parameter_offload", None)
+        if off is not None:
+            off._begin_iteration(None, None)       # close the recorded iteration
+            if not off.trace_complete:
+                return
+        self.compile_report = fn()
+        self._compile_fn = None
 
     def step(self, lr_kwargs=None):
         assert self.optimizer is not None, "must provide optimizer during init in order to use step"

@@ -102,6 +102,8 @@ def _convert(param: torch.nn.Parameter, group, remote_device: Optional[str], pin
 @torch.no_grad()
 def _partition_param(p, has_been_updated: bool = False):
     """Release the full tensor (first writing this rank's slice back if the full tensor was modified)."""
+    if p.ds_status == ZeroParamStatus.INFLIGHT and getattr(p, "_ds_inflight", None) is not None:
+        _wait_inflight(p)
     if p.ds_status != ZeroParamStatus.AVAILABLE:
         return
     if has_been_updated:
@@ -118,10 +120,16 @@ def _partition_param(p, has_been_updated: bool = False):
 
 
 @torch.no_grad()
-def all_gather_params(params: Iterable) -> None:
-    """Make the full tensors of ``params`` available (no-op for those that already are)."""
+def all_gather_params(params: Iterable, async_op: bool = False) -> None:
+    """Make the full tensors of ``params`` available (no-op for those that already are). ``async_op``: only LAUNCH the
+    collectives (status ``INFLIGHT``); a later blocking call on the same parameters waits for them. This is what the
+    trace-driven prefetcher uses to overlap the next modules' gathers with the current module's compute."""
     for p in params:
         if not is_zero_param(p) or p.ds_status == ZeroParamStatus.AVAILABLE:
+            continue
+        if p.ds_status == ZeroParamStatus.INFLIGHT:
+            if not async_op:
+                _wait_inflight(p)
             continue
         ws, _ = _group_info(p.ds_process_group)
         psize = p.ds_partition_numel
@@ -131,9 +139,21 @@ def all_gather_params(params: Iterable) -> None:
         else:
             full = torch.empty(psize * ws, dtype=local.dtype, device=p.ds_device)
             p.ds_status = ZeroParamStatus.INFLIGHT
-            dist.all_gather_into_tensor(full, local.contiguous(), group=p.ds_process_group)
+            work = dist.all_gather_into_tensor(full, local.contiguous(), group=p.ds_process_group, async_op=async_op)
+            if async_op:
+                p._ds_inflight = (work, full)
+                continue
         p.data = full.narrow(0, 0, p.ds_numel).view(p.ds_shape)
         p.ds_status = ZeroParamStatus.AVAILABLE
+
+
+def _wait_inflight(p) -> None:
+    work, full = p._ds_inflight
+    if work is not None:
+        work.wait()
+    p._ds_inflight = None
+    p.data = full.narrow(0, 0, p.ds_numel).view(p.ds_shape)
+    p.ds_status = ZeroParamStatus.AVAILABLE
 
 
 class Init:

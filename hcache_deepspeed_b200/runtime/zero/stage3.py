@@ -44,6 +44,18 @@ class DeepSpeedZeRoOffload:
         init._convert_module(module)
         self.hooks = []
         self.reduce_fn = None  # set by the optimizer: called with a list of params whose .grad is complete
+        # trace-driven prefetch (reference: partitioned_param_coordinator.py record_module / fetch_sub_module): the first
+        # iteration records the (module, phase) order; later iterations launch the gathers of the next modules, up to
+        # ``prefetch_bucket_size`` elements, while the current module computes. A diverging order drops the trace.
+        self.prefetch_bucket_size = int(prefetch_bucket_size)
+        self.max_live_parameters = int(max_live_parameters) or 2 ** 62
+        self.trace: List[tuple] = []            # [(module, phase)] of one forward(+backward)
+        self.trace_complete = False
+        self.prefetch_plan: Optional[List[List[torch.nn.Parameter]]] = None   # set by compile passes; else derived
+        self.event_times: List[float] = []      # perf_counter at each recorded event (profile for the passes)
+        self._recording: List[tuple] = []
+        self._pos = 0
+        self.stats = {"prefetched": 0, "trace_invalidations": 0}
         self._install(module)
 
     @staticmethod
@@ -54,6 +66,7 @@ class DeepSpeedZeRoOffload:
         return ps
 
     def _install(self, root: torch.nn.Module):
+        self.hooks.append(root.register_forward_pre_hook(self._begin_iteration))
         under_leaf = set()
         for m in root.modules():
             if id(m) in under_leaf:
@@ -73,11 +86,59 @@ class DeepSpeedZeRoOffload:
             if is_zero_param(p) and p.requires_grad:
                 self.hooks.append(p.register_post_accumulate_grad_hook(self._post_accumulate))
 
+    # ---- trace + prefetch ----------------------------------------------------------------------------------------
+    def _begin_iteration(self, m, args):
+        if not self.trace_complete and self._recording:
+            self.trace, self.trace_complete = self._recording, True
+            self.prefetch_plan = None
+        self._recording, self._pos = [], 0
+        if not self.trace_complete:
+            self.event_times = []
+
+    def reset_trace(self):
+        self.trace, self.trace_complete, self.prefetch_plan, self._recording, self._pos = [], False, None, [], 0
+
+    def _live_numel(self) -> int:
+        return sum(p.ds_numel for p in self.module.parameters()
+                   if is_zero_param(p) and not p.ds_persist and p.ds_status != ZeroParamStatus.NOT_AVAILABLE)
+
+    def _derive_plan(self) -> List[List[torch.nn.Parameter]]:
+        from ...compile.passes.prefetch import schedule_prefetch
+        return schedule_prefetch([(self._own_params(m), ph) for m, ph in self.trace], self.prefetch_bucket_size)
+
+    def _on_event(self, m, phase: str):
+        if not self.trace_complete:
+            import time
+            self._recording.append((m, phase))
+            self.event_times.append(time.perf_counter())
+            return
+        pos = self._pos
+        if pos >= len(self.trace) or self.trace[pos][0] is not m or self.trace[pos][1] != phase:
+            # the model took another path this time: stop trusting the trace and record again from the next iteration
+            self.stats["trace_invalidations"] += 1
+            self.reset_trace()
+            return
+        self._pos = pos + 1
+        if self.prefetch_bucket_size <= 0:
+            return
+        if self.prefetch_plan is None:
+            self.prefetch_plan = self._derive_plan()
+        ahead = self.prefetch_plan[pos]
+        if not ahead:
+            return
+        if phase == "fwd" and pos + 1 < len(self.trace) and self.trace[pos + 1][1] == "bwd" and not torch.is_grad_enabled():
+            return       # evaluation: there is no backward to prefetch for
+        todo = [p for p in ahead if p.ds_status == ZeroParamStatus.NOT_AVAILABLE]
+        if todo and self._live_numel() + sum(p.ds_numel for p in todo) <= self.max_live_parameters:
+            all_gather_params(todo, async_op=True)
+            self.stats["prefetched"] += len(todo)
+
     def _pre_forward(self, m, args):
         ps = self._own_params(m)
         all_gather_params(ps)
         for p in ps:
             p.ds_active_sub_modules.add(id(m))
+        self._on_event(m, "fwd")
 
     def _post_forward(self, m, args, out):
         self._release(m)
@@ -87,6 +148,7 @@ class DeepSpeedZeRoOffload:
         all_gather_params(ps)
         for p in ps:
             p.ds_active_sub_modules.add(id(m))
+        self._on_event(m, "bwd")
 
     def _post_accumulate(self, p):
         if self.reduce_fn is not None:
@@ -145,6 +207,8 @@ class DeepSpeedZeroOptimizer_Stage3:
         self.offload_optimizer = bool(off is not None and str(getattr(off, "device", "none")).split(".")[-1] == "cpu")
         dtype = next((p.dtype for p in module.parameters()), torch.float32)
         self.parameter_offload = DeepSpeedZeRoOffload(module, dp_process_group=dp_process_group,
+                                                      prefetch_bucket_size=prefetch_bucket_size,
+                                                      max_live_parameters=max_live_parameters,
                                                       param_persistence_threshold=param_persistence_threshold,
                                                       offload_param_config=offload_param_config, mpu=mpu, dtype=None)
         self.parameter_offload.reduce_fn = self._reduce_ready_grads

@@ -61,7 +61,14 @@ def zero_worker(rank, world, stage, steps, gas, offload, dtype_name, ckpt_dir):
     if os.environ.get("HDS_TEST_Z3_LEAF") == "1":
         from hcache_deepspeed_b200.utils.z3_leaf_module import get_z3_leaf_modules, set_z3_leaf_modules, z3_leaf_parameter
         assert set_z3_leaf_modules(model, ["Stack"]) == [model.layers]
+    compile_on = os.environ.get("HDS_TEST_Z3_COMPILE") == "1"
+    if compile_on:
+        cfg["compile"] = {"deepcompile": True, "selective_gather_budget_bytes": 3000, "prefetch_bucket_size": 100000,
+                          "offload_opt_states": True}
     engine, opt, _, _ = ds.initialize(model=model, config=cfg)
+    if compile_on:
+        assert engine.is_deepcompile_enabled() and not engine.is_compiled
+        engine.compile()
     if os.environ.get("HDS_TEST_Z3_LEAF") == "1":
         assert get_z3_leaf_modules(engine.module) == [engine.module.layers]
         assert all(z3_leaf_parameter(p) for p in engine.module.layers.parameters())
@@ -84,6 +91,11 @@ def zero_worker(rank, world, stage, steps, gas, offload, dtype_name, ckpt_dir):
         if ckpt_dir and step == steps // 2 - 1:
             engine.save_checkpoint(ckpt_dir, tag="mid", client_state={"note": 7})
     out = {"losses": losses, "global_steps": engine.global_steps}
+    if compile_on:
+        out["compile_report"] = engine.compile_report
+        if stage == 3:
+            out["prefetch_stats"] = dict(engine.optimizer.parameter_offload.stats)
+            out["persistent"] = sum(1 for p in engine.module.parameters() if p.ds_persist)
     if stage == 3:
         from hcache_deepspeed_b200.runtime.zero import GatheredParameters
         sd = {}

@@ -224,6 +224,26 @@ def test_zero3_leaf_module_2ranks(monkeypatch):
             torch.testing.assert_close(r["state"][k], v, rtol=2e-4, atol=2e-5)
 
 
+@pytest.mark.parametrize("stage", [3, 1])
+def test_schedule_compiler_2ranks(monkeypatch, stage):
+    """engine.compile(): after the profiled first step the passes apply a prefetch plan, persistent parameters and
+    optimizer-state offload; training results do not change."""
+    monkeypatch.setenv("HDS_TEST_Z3_COMPILE", "1")
+    steps, world = 5, 2
+    want, want_state = reference_run(steps=steps, global_bs=4 * world)
+    res = run_distributed(zero_worker, world, stage, steps, 1, False, "fp32", None)
+    for r in res:
+        for k, v in want_state.items():
+            torch.testing.assert_close(r["state"][k], v, rtol=2e-4, atol=2e-5)
+        rep = r["compile_report"]
+        assert rep is not None and rep["adam_state_bytes"] > 0
+        if stage == 3:
+            assert rep["events"] > 0 and rep["prefetch_launch_points"] > 0
+            assert rep["persistent_params"] > 0 and rep["persistent_bytes"] <= 2 * 3000
+            assert r["persistent"] == rep["persistent_params"]
+            assert r["prefetch_stats"]["prefetched"] > 0 and r["prefetch_stats"]["trace_invalidations"] == 0
+
+
 @pytest.mark.parametrize("stage,dtype", [(0, "bf16"), (2, "bf16"), (2, "fp16"), (0, "fp16")])
 def test_mixed_precision_trains(stage, dtype):
     res = run_distributed(zero_worker, 2, stage, 12, 1, False, dtype, None)

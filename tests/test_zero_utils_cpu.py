@@ -119,3 +119,52 @@ def test_runtime_name_parity_modules():
     assert config_utils.get_scalar_param({"a": 1}, "b", 7) == 7
     f = compiler.disable(lambda x: x + 1)
     assert f(1) == 2 and not compiler.is_compiling()
+
+
+def _fake_param(n, persist=False):
+    p = torch.nn.Parameter(torch.empty(0))
+    p.ds_numel, p.ds_persist = n, persist
+    return p
+
+
+def test_schedule_passes_on_a_synthetic_trace():
+    from hcache_deepspeed_b200.compile.list_schedule import peak_live_numel, schedule_gathers
+    from hcache_deepspeed_b200.compile.passes.prefetch import schedule_prefetch
+    from hcache_deepspeed_b200.compile.passes.selective_gather import selective_gather
+    from hcache_deepspeed_b200.compile.profilers import fit_alpha_beta
+    from hcache_deepspeed_b200.compile.trace import ModuleTrace, TraceEvent
+    a, b, c, d = _fake_param(100), _fake_param(4000), _fake_param(50, persist=True), _fake_param(1000)
+    order = [([a], "fwd"), ([b], "fwd"), ([c, d], "fwd"), ([c, d], "bwd"), ([b], "bwd"), ([a], "bwd")]
+    plan = [[id(p) for p in step] for step in schedule_prefetch(order, bucket_numel=4500)]
+    assert plan[0] == [id(b)]                  # d does not fit into what is left of the bucket after b
+    assert plan[1] == [id(d), id(a)]           # c is persistent: never prefetched; (c, d) of bwd is the same d
+    assert plan[2] == [id(b), id(a)] and plan[4] == [id(a)] and plan[-1] == []
+    assert schedule_prefetch(order, 0) == [[] for _ in order]
+    trace = ModuleTrace([TraceEvent(i, f"m{i}", ph, ps) for i, (ps, ph) in enumerate(order)])
+    assert trace.uses()[id(a)] == [0, 5]
+    # benefit per byte: the small parameter first; the budget stops before the big one
+    chosen = selective_gather(trace, budget_bytes=3000, world_size=2)
+    assert chosen[0] is a and any(x is d for x in chosen) and not any(x is b for x in chosen)
+    assert selective_gather(trace, 10 ** 9, world_size=1) == []
+    launch = schedule_gathers(trace, max_live_numel=4200)
+    assert any(x is b for x in launch[0]) and not any(x is c for v in launch.values() for x in v)
+    assert peak_live_numel(trace, launch) <= 4200 + 4000
+    fit = fit_alpha_beta([(1000, 1e-5 + 2000 / 1e9), (100000, 1e-5 + 200000 / 1e9), (10 ** 6, 1e-5 + 2e6 / 1e9)])
+    assert fit["alpha_s"] == pytest.approx(1e-5, rel=1e-3) and fit["bandwidth_Bps"] == pytest.approx(1e9, rel=1e-3)
+
+
+def test_adam_state_mover_wraps_step():
+    from hcache_deepspeed_b200.compile.passes.offload_adam_states import move_opt_states
+    lin = torch.nn.Linear(4, 4)
+    ref = torch.nn.Linear(4, 4)
+    ref.load_state_dict(lin.state_dict())
+    opt, opt_ref = torch.optim.Adam(lin.parameters(), lr=1e-2), torch.optim.Adam(ref.parameters(), lr=1e-2)
+    mover = move_opt_states(opt, "cpu", double_buffer=False)
+    for i in range(3):
+        x = torch.randn(2, 4)
+        for m, o in ((lin, opt), (ref, opt_ref)):
+            o.zero_grad()
+            m(x).sum().backward()
+            o.step()
+        assert mover.offloaded
+    assert torch.allclose(lin.weight, ref.weight) and mover.bytes_moved > 0
