@@ -204,7 +204,9 @@ class DeepSpeedZeroOptimizer_Stage3:
         self.custom_loss_scaler = False
         self.external_loss_scale = None
         off = offload_optimizer_config
-        self.offload_optimizer = bool(off is not None and str(getattr(off, "device", "none")).split(".")[-1] == "cpu")
+        off_dev = str(getattr(off, "device", "none")).split(".")[-1] if off is not None else "none"
+        self.offload_optimizer = off_dev in ("cpu", "nvme")
+        self.optimizer_swapper = None
         dtype = next((p.dtype for p in module.parameters()), torch.float32)
         self.parameter_offload = DeepSpeedZeRoOffload(module, dp_process_group=dp_process_group,
                                                       prefetch_bucket_size=prefetch_bucket_size,
@@ -233,6 +235,15 @@ class DeepSpeedZeroOptimizer_Stage3:
             master.requires_grad = True
             self.fp32_partitioned_groups_flat.append(master)
             group["params"] = [master]
+        if off_dev == "nvme":
+            # ZeRO-Infinity: master weights + optimizer state of each group live in files between steps
+            from ..swap_tensor import PartitionedOptimizerSwapper, PipelinedOptimizerSwapper
+            piped = bool(getattr(off, "pipeline_read", False) or getattr(off, "pipeline_write", False))
+            masters = [m for m in self.fp32_partitioned_groups_flat if m.numel()]
+            self.optimizer_swapper = (PipelinedOptimizerSwapper if piped else PartitionedOptimizerSwapper)(
+                off, aio_config if isinstance(aio_config, dict) else None, str(off.nvme_path), self.optimizer,
+                max((m.numel() for m in masters), default=0), "cpu", torch.float32, timers)
+            self.optimizer_swapper.initialize_parameters(masters, masters)
         if verbose and self.rank == 0:
             n = sum(p.ds_numel for g in self.fp16_groups for p in g)
             logger.info(f"ZeRO stage 3: {n} parameters over {self.partition_count} ranks, optimizer offload="
@@ -337,6 +348,8 @@ class DeepSpeedZeroOptimizer_Stage3:
             clip = (scaled_norm / prev + 1e-6) / self.clip_grad
             if clip > 1:
                 combined = clip * prev
+        if self.optimizer_swapper is not None:
+            return self._step_swapped(combined)
         for gi, params in enumerate(self.fp16_groups):
             master = self.fp32_partitioned_groups_flat[gi]
             if not params:
@@ -361,8 +374,70 @@ class DeepSpeedZeroOptimizer_Stage3:
                     p.ds_status = ZeroParamStatus.NOT_AVAILABLE
                     all_gather_params([p])
 
+    def _write_back(self, gi: int):
+        master, off = self.fp32_partitioned_groups_flat[gi], 0
+        master.grad = None
+        for p in self.fp16_groups[gi]:
+            n = p.ds_partition_numel
+            p.ds_tensor.copy_(master.detach().narrow(0, off, n).to(p.ds_tensor.dtype))
+            off += n
+            if p.ds_status == ZeroParamStatus.AVAILABLE:  # persistent parameters: refresh the resident full copy
+                p.ds_status = ZeroParamStatus.NOT_AVAILABLE
+                all_gather_params([p])
+
+    def _step_swapped(self, combined: float):
+        """Optimizer step with the NVMe tier: group by group, swap in (the next group's read already in flight) ->
+        update -> write back the low-precision slices -> swap out (asynchronously with a pipelined swapper)."""
+        sw = self.optimizer_swapper
+        live = [gi for gi, params in enumerate(self.fp16_groups) if params]
+        all_groups = self.optimizer.param_groups
+        try:
+            for k, gi in enumerate(live):
+                master = self.fp32_partitioned_groups_flat[gi]
+                nxt = self.fp32_partitioned_groups_flat[live[k + 1]] if k + 1 < len(live) else None
+                sw.swap_in_optimizer_state(master, async_parameter=nxt)
+                grads = []
+                for p in self.fp16_groups[gi]:
+                    g = self.grad_partitions.get(p.ds_id)
+                    grads.append(g.float().to(master.device) if g is not None else
+                                 torch.zeros(p.ds_partition_numel, dtype=torch.float32, device=master.device))
+                master.grad = torch.cat(grads).div_(combined)
+                self.optimizer.param_groups = [all_groups[gi]]
+                self.optimizer.step()
+                self._write_back(gi)
+                sw.swap_out_optimizer_state(master, async_swap=True)
+        finally:
+            self.optimizer.param_groups = all_groups
+        self.grad_partitions = {}
+
+    class _Resident:
+        """Everything swapped in for the duration (checkpoint save / load, consolidation)."""
+
+        def __init__(self, opt):
+            self.opt = opt
+
+        def __enter__(self):
+            sw = self.opt.optimizer_swapper
+            if sw is not None:
+                sw.swap_in_all([m for m in self.opt.fp32_partitioned_groups_flat if id(m) in sw.records])
+
+        def __exit__(self, *exc):
+            sw = self.opt.optimizer_swapper
+            if sw is not None:
+                sw.swap_out_all([m for m in self.opt.fp32_partitioned_groups_flat if id(m) in sw.records])
+                sw.purge_state()
+            return False
+
     # ---------------------------------------------------------------------------------------------
     def state_dict(self):
+        with self._Resident(self):
+            sd = self._state_dict()
+            if self.optimizer_swapper is not None:     # the live state tensors are about to be swapped out again
+                import copy
+                sd["optimizer_state_dict"] = copy.deepcopy(sd["optimizer_state_dict"])
+            return sd
+
+    def _state_dict(self):
         return {"loss_scaler": self.loss_scaler, "dynamic_loss_scale": self.dynamic_loss_scale, "overflow": self.overflow,
                 "partition_count": self.partition_count, "zero_stage": 3,
                 "optimizer_state_dict": self.optimizer.state_dict(),
@@ -370,8 +445,12 @@ class DeepSpeedZeroOptimizer_Stage3:
                 "param_shapes": [{self.param_names.get(p, f"group{gi}_param{i}"): tuple(p.ds_shape)
                                   for i, p in enumerate(params)} for gi, params in enumerate(self.fp16_groups)]}
 
-    def load_state_dict(self, state_dict_list, load_optimizer_states=True, load_from_fp32_weights=False,
-                        checkpoint_folder=None, load_serial=None, param_shapes=None):
+    def load_state_dict(self, *args, **kw):
+        with self._Resident(self):
+            return self._load_state_dict(*args, **kw)
+
+    def _load_state_dict(self, state_dict_list, load_optimizer_states=True, load_from_fp32_weights=False,
+                         checkpoint_folder=None, load_serial=None, param_shapes=None):
         sd = state_dict_list[self.rank] if isinstance(state_dict_list, (list, tuple)) else state_dict_list
         if sd.get("partition_count", self.partition_count) != self.partition_count:
             raise RuntimeError("ZeRO-3 checkpoints can only be loaded with the data-parallel size they were saved with")
@@ -392,6 +471,10 @@ class DeepSpeedZeroOptimizer_Stage3:
                     all_gather_params([p])
 
     def get_fp32_state_dict_on_rank0(self):
+        with self._Resident(self):
+            return self._get_fp32_state_dict_on_rank0()
+
+    def _get_fp32_state_dict_on_rank0(self):
         """Gather full fp32 parameters (for ``save_16bit_model`` / consolidation)."""
         out = {}
         for gi, params in enumerate(self.fp16_groups):

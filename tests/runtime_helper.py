@@ -52,7 +52,12 @@ def zero_worker(rank, world, stage, steps, gas, offload, dtype_name, ckpt_dir):
     cfg = {"train_micro_batch_size_per_gpu": micro, "gradient_accumulation_steps": gas,
            "optimizer": {"type": "AdamW", "params": {"lr": 1e-2, "weight_decay": 0.0}},
            "zero_optimization": {"stage": stage, "stage3_param_persistence_threshold": 0}, "steps_per_print": 1000}
-    if offload:
+    if offload == "nvme":
+        import tempfile
+        cfg["zero_optimization"]["offload_optimizer"] = {"device": "nvme", "pipeline_read": True, "pipeline_write": True,
+                                                         "nvme_path": tempfile.mkdtemp(prefix=f"hds_optswap_r{rank}_")}
+        cfg["aio"] = {"block_size": 4096}
+    elif offload:
         cfg["zero_optimization"]["offload_optimizer"] = {"device": "cpu"}
     if dtype_name == "bf16":
         cfg["bf16"] = {"enabled": True}
@@ -91,6 +96,10 @@ def zero_worker(rank, world, stage, steps, gas, offload, dtype_name, ckpt_dir):
         if ckpt_dir and step == steps // 2 - 1:
             engine.save_checkpoint(ckpt_dir, tag="mid", client_state={"note": 7})
     out = {"losses": losses, "global_steps": engine.global_steps}
+    if offload == "nvme":
+        sw = engine.optimizer.optimizer_swapper
+        out["swap_stats"] = dict(sw.stats)
+        out["masters_resident"] = [m.numel() for m in engine.optimizer.fp32_partitioned_groups_flat]
     if compile_on:
         out["compile_report"] = engine.compile_report
         if stage == 3:

@@ -224,6 +224,20 @@ def test_zero3_leaf_module_2ranks(monkeypatch):
             torch.testing.assert_close(r["state"][k], v, rtol=2e-4, atol=2e-5)
 
 
+def test_zero3_nvme_optimizer_swapper_2ranks(tmp_path):
+    """ZeRO-Infinity: fp32 masters + Adam moments live in files between steps (pipelined swapper); same training
+    result, checkpoint resume included."""
+    steps, world = 6, 2
+    want, want_state = reference_run(steps=steps, global_bs=4 * world)
+    res = run_distributed(zero_worker, world, 3, steps, 1, "nvme", "fp32", str(tmp_path / "ckpt"))
+    for r in res:
+        for k, v in want_state.items():
+            torch.testing.assert_close(r["state"][k], v, rtol=2e-4, atol=2e-5)
+        assert r["resumed_losses"] == pytest.approx(r["losses"][steps // 2:], rel=1e-4, abs=1e-5)
+        assert r["swap_stats"]["bytes_read"] > 0 and r["swap_stats"]["bytes_written"] > 0
+        assert all(n == 0 for n in r["masters_resident"])      # nothing resident between steps
+
+
 @pytest.mark.parametrize("stage", [3, 1])
 def test_schedule_compiler_2ranks(monkeypatch, stage):
     """engine.compile(): after the profiled first step the passes apply a prefetch plan, persistent parameters and

@@ -168,3 +168,41 @@ def test_adam_state_mover_wraps_step():
             o.step()
         assert mover.offloaded
     assert torch.allclose(lin.weight, ref.weight) and mover.bytes_moved > 0
+
+
+@pytest.mark.parametrize("pipelined", [False, True])
+def test_optimizer_swapper_roundtrip(tmp_path, pipelined):
+    from hcache_deepspeed_b200.runtime.swap_tensor import PartitionedOptimizerSwapper, PipelinedOptimizerSwapper
+    torch.manual_seed(0)
+    masters = [torch.randn(n, requires_grad=True) for n in (3000, 1000, 5000)]
+    twins = [m.detach().clone().requires_grad_(True) for m in masters]
+    opt = torch.optim.Adam([{"params": [m]} for m in masters], lr=1e-2)
+    ref = torch.optim.Adam([{"params": [m]} for m in twins], lr=1e-2)
+    cls = PipelinedOptimizerSwapper if pipelined else PartitionedOptimizerSwapper
+    sw = cls(None, {"block_size": 4096}, str(tmp_path), opt, 5000, "cpu", torch.float32, None, buffer_count=4)
+    sw.initialize_parameters(masters, masters)
+    assert all(m.numel() == 0 for m in masters)
+    groups = opt.param_groups
+    for it in range(3):
+        grads = [torch.randn(n) for n in (3000, 1000, 5000)]
+        for i, m in enumerate(masters):
+            sw.swap_in_optimizer_state(m, async_parameter=masters[i + 1] if i + 1 < len(masters) else None)
+            assert m.numel() == grads[i].numel()
+            m.grad = grads[i].clone()
+            opt.param_groups = [groups[i]]
+            opt.step()
+            m.grad = None
+            sw.swap_out_optimizer_state(m, async_swap=True)
+            assert m.numel() == 0 and opt.state[m]["exp_avg"].numel() == 0
+        opt.param_groups = groups
+        for t, g in zip(twins, grads):
+            t.grad = g.clone()
+        ref.step()
+    sw.swap_in_all(masters)
+    for m, t in zip(masters, twins):
+        torch.testing.assert_close(m.detach(), t.detach())
+        torch.testing.assert_close(opt.state[m]["exp_avg_sq"], ref.state[t]["exp_avg_sq"])
+    assert sw.stats["bytes_read"] > 0 and sw.swappable_tensor(numel=10 ** 7) and not sw.swappable_tensor(numel=10)
+    sw.swap_out_all(masters)
+    sw.purge_state()
+    assert len(sw._free) == 4
