@@ -413,3 +413,60 @@ def test_top_level_namespace_mirrors_deepspeed():
     assert hasattr(ds.zero, "Init") and hasattr(ds.pipe, "PipelineModule") and not ds.is_compile_supported()
     with pytest.raises(AttributeError):
         ds.no_such_thing
+
+
+def test_linear_init_context_and_domino_linears():
+    from hcache_deepspeed_b200.linear import Init, LoRAConfig, LoRAOptimizedLinear
+    from hcache_deepspeed_b200.runtime.domino import DominoAsyncColumnParallelLinear, RowParallelLinearNoComm
+    with Init(lora_config=LoRAConfig(lora_r=4), dtype=torch.float32) as ctx:
+        m = torch.nn.Sequential(torch.nn.Linear(16, 32, bias=False), torch.nn.ReLU(), torch.nn.Linear(32, 8))
+    assert isinstance(m[0], LoRAOptimizedLinear) and type(m[2]) is torch.nn.Linear and torch.nn.Linear.__name__ == "Linear"
+    ctx.finalize(m)
+    assert sorted(n for n, p in m.named_parameters() if p.requires_grad) == ["0.lora_weight_1.weight", "0.lora_weight_2.weight"]
+    m(torch.randn(2, 16)).sum().backward()
+    # single-process Domino linears == plain linears; the handle dict stays empty without a tensor-parallel group
+    torch.manual_seed(0)
+    col, row = DominoAsyncColumnParallelLinear(8, 12, bias=True), RowParallelLinearNoComm(12, 8, bias=True)
+    x = torch.randn(3, 8, requires_grad=True)
+    handles = {}
+    h, _ = col(x, handles, 0)
+    y, b = row(torch.relu(h))
+    (y + b).sum().backward()
+    ref = torch.nn.functional.linear(torch.relu(torch.nn.functional.linear(x, col.weight, col.bias)), row.weight, row.bias)
+    assert torch.allclose(y + b, ref, atol=1e-6) and handles == {} and x.grad is not None and col.weight.grad is not None
+
+
+def test_module_quantize_and_launcher_helper(monkeypatch):
+    from types import SimpleNamespace
+
+    from hcache_deepspeed_b200.launcher.launcher_helper import build_command, env_mapping, parse_args
+    from hcache_deepspeed_b200.module_inject.module_quantize import quantize_transformer_layer
+
+    class Layer(torch.nn.Module):
+        def __init__(self):
+            super().__init__()
+            lin = lambda: torch.nn.Linear(8, 8)  # noqa: E731
+            self.attention = torch.nn.Module()
+            self.attention.self = torch.nn.Module()
+            self.attention.self.query, self.attention.self.key, self.attention.self.value = lin(), lin(), lin()
+            self.attention.output = torch.nn.Module()
+            self.attention.output.dense = lin()
+            self.intermediate = torch.nn.Module()
+            self.intermediate.dense = lin()
+            self.output = torch.nn.Module()
+            self.output.dense = lin()
+
+    model = torch.nn.Sequential(Layer(), Layer())
+    w0 = model[0].attention.self.query.weight.detach().clone()
+    scales = quantize_transformer_layer(Layer, model)
+    q = model[0].attention.self.query.weight
+    assert len(scales) == 12 and q.dtype == torch.int8 and (q.float() * scales[0] - w0).abs().max() <= scales[0] / 2 + 1e-7
+    env = env_mapping({"OMPI_COMM_WORLD_RANK": "3", "PMI_RANK": "3", "OMPI_COMM_WORLD_LOCAL_RANK": "1"})
+    assert env["RANK"] == "3" and env["LOCAL_RANK"] == "1"
+    with pytest.raises(EnvironmentError):
+        env_mapping({"OMPI_COMM_WORLD_RANK": "3", "PMI_RANK": "2", "SLURM_LOCALID": "0"})
+    with pytest.raises(EnvironmentError):
+        env_mapping({})
+    args = parse_args(["--module", "pkg.train", "--lr", "1"])
+    cmd = build_command(args)
+    assert cmd[-4:] == ["-m", "pkg.train", "--lr", "1"]
