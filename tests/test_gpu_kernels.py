@@ -453,3 +453,51 @@ def test_gemm_2sm(dtype, M, N, K_, bn, mode):
     out = K().gemm_2sm(a, w, bias=b, act=3 if gated else 2, gated=gated, bn=bn)
     want = ref.gemm(a, w, bias=b, act=3 if gated else 2, gated=gated, out_dtype=torch.float32)
     torch.testing.assert_close(out.float(), want, **tol(dtype))
+
+
+def test_v2_kernel_wrapper_objects_cuda_vs_host():
+    """inference.v2.kernels wrapper classes: the CUDA path (native kernels) against their own host formulation."""
+    from hcache_deepspeed_b200.inference.v2.kernels import (BlasLibLinear, CUDAFPPreLN, CUDARMSNorm, MoEGather, MoEGEMM,
+                                                            MoEScatter, RaggedLogitsGather, RaggedTopKGating)
+    torch.manual_seed(5)
+    T, H, I, E, k = 70, 256, 384, 8, 2
+    x = rand(T, H)
+    gate_w = rand(E, H, scale=H ** -0.5)
+    w1, w2 = rand(E, 2 * I, H, scale=H ** -0.5), rand(E, H, I, scale=I ** -0.5)
+
+    lg = torch.empty(T, E, dtype=x.dtype, device="cuda")
+    BlasLibLinear(x.dtype)(lg, x, gate_w)
+    torch.testing.assert_close(lg.float(), x.float() @ gate_w.float().t(), rtol=2e-2, atol=2e-2)
+    # one set of fp32 logits for both devices, ties broken, so both route identically
+    shared_logits = lg.float() + torch.arange(E, device="cuda") * 1e-4
+
+    def run(dev):
+        xd, a, b = x.to(dev), w1.to(dev), w2.to(dev)
+        logits = shared_logits.to(dev)
+        counts = torch.zeros(E, dtype=torch.int32, device=dev)
+        scores = torch.empty(T, k, dtype=torch.float32, device=dev)
+        ids, offs, slots = (torch.empty(T, k, dtype=torch.int32, device=dev) for _ in range(3))
+        RaggedTopKGating(xd.dtype)(counts, scores, ids, offs, logits)
+        rows = int(((counts + 127) // 128 * 128).sum())
+        xs = torch.zeros(rows, H, dtype=xd.dtype, device=dev)
+        cum = torch.zeros(E + 1, dtype=torch.int32, device=dev)
+        MoEScatter(xd.dtype)(xs, cum, slots, xd, counts, ids, offs)
+        hs = torch.zeros(rows, I, dtype=xd.dtype, device=dev)
+        ys = torch.zeros(rows, H, dtype=xd.dtype, device=dev)
+        MoEGEMM(xd.dtype, "silu", gated=True)(hs, xs, a, cum)
+        MoEGEMM(xd.dtype)(ys, hs, b, cum)
+        out = torch.zeros(T, H, dtype=torch.float32, device=dev)
+        MoEGather(xd.dtype)(out, ys, scores, slots)
+        gamma, beta = torch.ones(H, dtype=xd.dtype, device=dev), torch.zeros(H, dtype=xd.dtype, device=dev)
+        n1 = torch.empty_like(xd)
+        CUDARMSNorm(H, xd.dtype, 1e-6)(n1, xd, gamma)
+        zr, zh = torch.empty_like(xd), torch.empty_like(xd)
+        CUDAFPPreLN(H, xd.dtype, 1e-5)(zr, zh, xd, n1, gamma, beta)
+        last = torch.empty(3, H, dtype=xd.dtype, device=dev)
+        RaggedLogitsGather(H, xd.dtype)(last, zh, torch.tensor([0, 9, T - 1], dtype=torch.int32, device=dev))
+        return out.cpu(), n1.float().cpu(), zh.float().cpu(), last.float().cpu()
+
+    got, want = run("cuda"), run("cpu")
+    torch.testing.assert_close(got[0], want[0], rtol=4e-2, atol=4e-2)
+    for g_, w_ in zip(got[1:], want[1:]):
+        torch.testing.assert_close(g_, w_, rtol=2e-2, atol=2e-2)

@@ -93,3 +93,32 @@ def test_ragged_embed_gather_atoms_and_mixed_gemm():
     packed = (q4[:, 0::2] | (q4[:, 1::2] << 4)).to(torch.uint8)
     MixedGEMM(torch.float32, num_bits=4)(o, x, packed, s4)
     torch.testing.assert_close(o, x @ ((q4.float() - 8) * s4[:, None]).t(), atol=1e-5, rtol=1e-5)
+
+
+def test_v2_reference_import_paths():
+    from hcache_deepspeed_b200.inference.v2.model_implementations.flat_model_helpers import (flatten_inference_model,  # noqa: F401
+                                                                                             make_param_filename)
+    from hcache_deepspeed_b200.inference.v2.model_implementations.inference_policy_base import ContainerMap
+    from hcache_deepspeed_b200.inference.v2.model_implementations.inference_transformer_base import DSTransformerModelBase  # noqa: F401
+    from hcache_deepspeed_b200.inference.v2.model_implementations.sharding import ShardingType, shard_mlp_1_param
+    from hcache_deepspeed_b200.inference.v2.modules.interfaces import DSLinearBase, DSLinearRegistry  # noqa: F401
+    from hcache_deepspeed_b200.inference.v2.modules.module_registry import DSModuleRegistryBase
+    assert issubclass(DSLinearRegistry, DSModuleRegistryBase) and ShardingType.OUTER_DIMENSION.value == 0
+    w = torch.arange(128.0 * 4).view(128, 4)
+    assert shard_mlp_1_param(w, 1, 2).shape[0] == 64 and make_param_filename("/x", 0, 2).startswith("/x")
+
+    class C:
+        def __init__(self):
+            self.got = {}
+
+        def set_dependency(self, n, t):
+            self.got[n] = t
+
+    m, layers, nt = ContainerMap(), [C(), C()], C()
+    m.set_transformer_params(["model.layers"], layers)
+    m.set_non_transformer_params(nt)
+    m.set_unmapped_params(["rotary"])
+    m.map_param("model.layers.1.self_attn.q_proj.weight", 1)
+    m.map_param("model.embed_tokens.weight", 2)
+    m.map_param("rotary.inv_freq", 3)
+    assert layers[1].got == {"self_attn.q_proj.weight": 1} and nt.got == {"model.embed_tokens.weight": 2} and layers[0].got == {}
