@@ -8,6 +8,8 @@ bootstrap / cold-path plumbing and the NCCL baseline.
 """
 from __future__ import annotations
 
+import functools
+
 import os
 from datetime import timedelta
 from typing import Any, List, Optional
@@ -45,6 +47,7 @@ def _msg_size(args, kwargs) -> int:
 def timed_op(func):
     """Record latency + message size of a collective when the comms logger is on (forces a device sync)."""
 
+    @functools.wraps(func)
     def wrapper(*args, **kwargs):
         prof = comms_logger.enabled and (kwargs.pop("prof", False) or comms_logger.prof_all
                                          or kwargs.get("log_name", func.__name__) in comms_logger.prof_ops)

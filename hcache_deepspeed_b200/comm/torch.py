@@ -1,0 +1,84 @@
+"""``TorchBackend`` (``deepspeed/comm/torch.py:96-420``): the ``torch.distributed`` transport as an object. Every
+collective of the functional API is available as a method (delegating to :mod:`.comm`, so the comms logger sees them),
+plus the capability probes the ZeRO code asks before picking a collective."""
+from __future__ import annotations
+
+import os
+from typing import Optional
+
+import torch
+import torch.distributed as tdist
+
+from . import comm as _c
+from .backend import Backend
+
+_DELEGATED = ["broadcast", "all_gather", "all_gather_into_tensor", "all_gather_coalesced", "reduce_scatter_tensor", "reduce_scatter",
+              "all_to_all_single", "all_to_all", "send", "recv", "isend", "irecv", "gather", "scatter", "barrier",
+              "monitored_barrier", "reduce", "all_reduce", "inference_all_reduce", "all_reduce_coalesced", "get_rank",
+              "get_world_size", "get_global_rank", "get_world_group", "get_all_ranks_from_group", "new_group",
+              "destroy_process_group", "is_available"]
+
+
+def get_coalescing_manager(group, device, reqs, async_op: bool = False):
+    return tdist._coalescing_manager(group, device=device, async_ops=async_op)
+
+
+class TorchBackend(Backend):
+
+    def __init__(self, backend: str = "nccl", timeout=None, init_method: Optional[str] = None, rank: int = -1, world_size: int = -1,
+                 name: str = "torch"):
+        super().__init__(name=name)
+        self.using_mpi = False
+        if not tdist.is_initialized():
+            kw = {"timeout": timeout} if timeout is not None else {}
+            tdist.init_process_group(backend, init_method=init_method, rank=rank, world_size=world_size, **kw)
+        self.initialized = True
+        self.world_rank, self.world_size = tdist.get_rank(), tdist.get_world_size()
+        self.world_group = tdist.group.WORLD
+        self.backend_name = tdist.get_backend()
+
+    # ---- capability probes -----------------------------------------------------------------------------------------
+    @classmethod
+    def has_all_gather_into_tensor(cls) -> bool:
+        return hasattr(tdist, "all_gather_into_tensor")
+
+    @classmethod
+    def has_reduce_scatter_tensor(cls) -> bool:
+        return hasattr(tdist, "reduce_scatter_tensor")
+
+    def has_all_reduce_coalesced(self) -> bool:
+        return hasattr(tdist, "all_reduce_coalesced")
+
+    def has_coalescing_manager(self) -> bool:
+        return hasattr(tdist, "_coalescing_manager")
+
+    def is_initialized(self) -> bool:
+        return tdist.is_initialized()
+
+    def get_backend(self, group=None) -> str:
+        return tdist.get_backend(group)
+
+    def get_local_rank(self) -> int:
+        return int(os.environ.get("LOCAL_RANK", 0))
+
+    def init_device_mesh(self, mesh_shape, mesh_dim_names):
+        from torch.distributed.device_mesh import init_device_mesh
+        return init_device_mesh("cuda" if torch.cuda.is_available() else "cpu", tuple(mesh_shape), mesh_dim_names=tuple(mesh_dim_names))
+
+    def enable_symm_mem_for_group(self, group_name: str):
+        return _c.enable_symm_mem_for_group(group_name)
+
+
+def _delegate(name):
+    fn = getattr(_c, name)
+
+    def method(self, *a, **k):
+        return fn(*a, **k)
+
+    method.__name__ = name
+    method.__doc__ = fn.__doc__
+    return method
+
+
+for _n in _DELEGATED:
+    setattr(TorchBackend, _n, _delegate(_n))

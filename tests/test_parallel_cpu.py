@@ -100,3 +100,28 @@ def test_shm_allreduce_matches_gloo(world):
         assert r["torch.bfloat16_3001"] < 0.07        # one bf16 rounding of an fp32 sum vs gloo's pairwise bf16 adds
         assert r["int_fallback"] == world
     assert len({r["name"] for r in res}) == 1 and not os.path.exists("/dev/shm/" + res[0]["name"])
+
+
+def _torch_backend_worker(rank, world):
+    import torch
+    import hcache_deepspeed_b200 as ds
+    from hcache_deepspeed_b200.comm import comm as c
+    from hcache_deepspeed_b200.comm.torch import TorchBackend
+    from hcache_deepspeed_b200.comm.utils import (get_local_rank_from_launcher, get_msg_size_from_args,
+                                                  get_world_rank_from_launcher, get_world_size_from_launcher)
+    ds.init_distributed(dist_backend="gloo")
+    b = TorchBackend("gloo")
+    t = torch.full((4,), float(rank + 1))
+    b.all_reduce(t)
+    out = torch.empty(2 * world)
+    b.all_gather_into_tensor(out, torch.full((2,), float(rank)))
+    assert b.is_initialized() and b.get_backend() == "gloo" and b.has_all_gather_into_tensor() and b.has_reduce_scatter_tensor()
+    assert get_world_rank_from_launcher() == rank and get_world_size_from_launcher() == world and get_local_rank_from_launcher() == rank
+    return {"sum": t.tolist(), "gathered": out.tolist(), "size": b.get_world_size(),
+            "msg": get_msg_size_from_args(c.all_reduce, t)}
+
+
+def test_torch_backend_object_2ranks():
+    res = run_distributed(_torch_backend_worker, 2)
+    for r in res:
+        assert r["sum"] == [3.0] * 4 and r["gathered"] == [0.0, 0.0, 1.0, 1.0] and r["size"] == 2 and r["msg"] == 16
