@@ -470,3 +470,44 @@ def test_module_quantize_and_launcher_helper(monkeypatch):
     args = parse_args(["--module", "pkg.train", "--lr", "1"])
     cmd = build_command(args)
     assert cmd[-4:] == ["-m", "pkg.train", "--lr", "1"]
+
+
+def test_compression_named_quantizers_and_helpers():
+    from hcache_deepspeed_b200.compression.helper import (convert_conv1d_to_linear, get_compress_methods, get_module_name,
+                                                          module_replacement, recursive_getattr)
+    from hcache_deepspeed_b200.compression.utils import AsymQuantizer, BinaryQuantizer, SymQuantizer, TernaryQuantizer
+    torch.manual_seed(0)
+    x = torch.randn(4, 16, requires_grad=True)
+    for Q in (SymQuantizer, AsymQuantizer):
+        y = Q.apply(x, 8, None, None, 2)
+        assert (y - x).abs().max() < 0.05
+        y.sum().backward()
+        assert torch.equal(x.grad, torch.ones_like(x))      # straight-through
+        x.grad = None
+        z = Q.apply(x.detach(), 4, -2.0, 2.0, 1)
+        assert z.unique().numel() <= 16
+    assert TernaryQuantizer.apply(x.detach(), 2, None, None, 1).unique().numel() <= 3
+    assert BinaryQuantizer.apply(x.detach(), 1, None, None, 1).unique().numel() <= 2
+    m = torch.nn.Sequential(torch.nn.Linear(4, 4), torch.nn.ReLU(), torch.nn.Linear(4, 2))
+    w0 = m[0].weight.detach().clone()
+    new = module_replacement(m, "0")
+    assert type(new).__name__ == "LinearLayer_Compress" and torch.equal(recursive_getattr(m, "0").weight, w0)
+    names, seen = get_module_name("g", m, r"^2$", set())
+    assert names == ["2"] and seen == {"2"}
+    methods = get_compress_methods(m, {"weight_quantization": {"shared_parameters": {"enabled": True, "quantizer_kernel": False},
+                                                                "different_groups": {"wq1": {"params": {"target_bits": 4}, "modules": ["0"]}}}})
+    assert methods[0][0] == ["0"] and methods[0][2]["weight_quantization"]["target_bits"] == 4
+
+    class Conv1D(torch.nn.Module):
+        def __init__(self):
+            super().__init__()
+            self.weight, self.bias = torch.nn.Parameter(torch.randn(6, 3)), torch.nn.Parameter(torch.randn(3))
+
+        def forward(self, x):
+            return x @ self.weight + self.bias
+
+    net = torch.nn.Sequential(Conv1D())
+    inp = torch.randn(2, 6)
+    want = net(inp)
+    convert_conv1d_to_linear(net, Conv1D)
+    assert isinstance(net[0], torch.nn.Linear) and torch.allclose(net(inp), want, atol=1e-6)
