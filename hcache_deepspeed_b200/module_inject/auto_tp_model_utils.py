@@ -1,0 +1,51 @@
+"""ALiBi helpers for auto-TP of BLOOM-style models (``deepspeed/module_inject/auto_tp_model_utils.py``): each rank
+needs the ALiBi slopes of ITS heads only."""
+from __future__ import annotations
+
+import math
+
+import torch
+
+from .. import comm as dist
+
+
+def _slopes(n_heads: int) -> torch.Tensor:
+    closest = 2 ** math.floor(math.log2(n_heads))
+    base = 2.0 ** (-(2.0 ** -(math.log2(closest) - 3)))
+    s = torch.pow(torch.tensor(base), torch.arange(1, 1 + closest, dtype=torch.float32))
+    if closest != n_heads:
+        extra_base = 2.0 ** (-(2.0 ** -(math.log2(2 * closest) - 3)))
+        n_rem = min(closest, n_heads - closest)
+        s = torch.cat([s, torch.pow(torch.tensor(extra_base), torch.arange(1, 1 + 2 * n_rem, 2, dtype=torch.float32))])
+    return s
+
+
+def build_bloom_alibi_tensor(attention_mask: torch.Tensor, num_heads: int, dtype: torch.dtype) -> torch.Tensor:
+    """``[batch * local_heads, 1, seq]`` ALiBi bias; under tensor parallelism only this rank's head slice."""
+    batch, seq = attention_mask.shape
+    slopes = _slopes(num_heads).to(attention_mask.device)
+    pos = ((attention_mask.cumsum(dim=-1) - 1) * attention_mask)[:, None, :]
+    alibi = slopes[None, :, None] * pos                       # [batch, heads, seq]
+    if dist.is_initialized() and dist.get_world_size() > 1:
+        per = num_heads // dist.get_world_size()
+        r = dist.get_rank()
+        alibi = alibi[:, r * per:(r + 1) * per]
+        num_heads = per
+    return alibi.reshape(batch * num_heads, 1, seq).to(dtype)
+
+
+def get_alibi_mask(self, tensor, seq_length_with_past):
+    """Baichuan-style cached ALiBi mask, sliced to this rank's heads."""
+    mask = self._get_alibi_mask_orig(tensor, seq_length_with_past) if hasattr(self, "_get_alibi_mask_orig") else None
+    if mask is not None and dist.is_initialized() and dist.get_world_size() > 1:
+        per = mask.shape[0] // dist.get_world_size()
+        mask = mask[dist.get_rank() * per:(dist.get_rank() + 1) * per]
+    return mask
+
+
+def build_mpt_alibi_tensor(self, *args, **kwargs):
+    alibi = self.build_mpt_alibi_tensor_orig(*args, **kwargs)
+    if dist.is_initialized() and dist.get_world_size() > 1:
+        per = alibi.shape[1] // dist.get_world_size()
+        alibi = alibi[:, dist.get_rank() * per:(dist.get_rank() + 1) * per]
+    return alibi

@@ -196,3 +196,33 @@ def test_custom_parameter_with_list():
     assert isinstance(layer.s, Stack)
     layer.set_dependency("part.1.w", torch.ones(2))
     assert torch.Tensor(layer.s).tolist() == [[0, 0], [2, 2], [4, 4]]
+
+
+def test_training_kernel_injection_bert_and_policy_tables():
+    """module_inject.inject: HF BERT layers -> fused training transformer layers with the same output."""
+    import torch
+    from transformers import BertConfig
+    from transformers.models.bert.modeling_bert import BertEncoder, BertLayer
+
+    from hcache_deepspeed_b200.model_implementations.transformers.ds_bert import DeepSpeedBERTInference  # noqa: F401
+    from hcache_deepspeed_b200.module_inject import replace_policy
+    from hcache_deepspeed_b200.module_inject.auto_tp_model_utils import build_bloom_alibi_tensor
+    from hcache_deepspeed_b200.module_inject.inject import module_inject
+    from hcache_deepspeed_b200.module_inject.utils import policy_to_ds_container
+    torch.manual_seed(0)
+    cfg = BertConfig(hidden_size=32, num_attention_heads=4, intermediate_size=64, num_hidden_layers=2, hidden_dropout_prob=0.0,
+                     attention_probs_dropout_prob=0.0, hidden_act="gelu")
+    cfg._attn_implementation = "eager"
+    enc = BertEncoder(cfg).eval()
+    x = torch.randn(2, 8, 32)
+    want = enc(x).last_hidden_state
+    module_inject(BertLayer, enc, cfg, 2, 8, 0, preln=False, fp16=False)
+    h = x
+    for layer in enc.layer:
+        assert type(layer).__name__ == "DeepSpeedTransformerLayer"
+        out = layer(h)
+        h = out[0] if isinstance(out, tuple) else out
+    torch.testing.assert_close(h, want, atol=1e-5, rtol=1e-5)
+    assert len(replace_policy.replace_policies) >= 8 and policy_to_ds_container(block="GPT2Block").__name__ == "gpt2"
+    a = build_bloom_alibi_tensor(torch.ones(2, 5, dtype=torch.long), 8, torch.float32)
+    assert a.shape == (16, 1, 5) and torch.allclose(a[0, 0], torch.arange(5.0) * 0.5)
