@@ -511,3 +511,29 @@ def test_compression_named_quantizers_and_helpers():
     want = net(inp)
     convert_conv1d_to_linear(net, Conv1D)
     assert isinstance(net[0], torch.nn.Linear) and torch.allclose(net(inp), want, atol=1e-6)
+
+
+def test_small_reference_named_modules():
+    import hcache_deepspeed_b200.inference.v2.inference_utils as iu
+    import hcache_deepspeed_b200.ops.fp_quantizer.fp8_gemm as fg
+    import hcache_deepspeed_b200.runtime.tensor_parallel.config as tc
+    import hcache_deepspeed_b200.utils.config as uc
+    from hcache_deepspeed_b200.inference.v2.logging import inference_logger
+    from hcache_deepspeed_b200.ops.fp_quantizer import FP_Quantize
+    from hcache_deepspeed_b200.runtime.activation_checkpointing.config import get_activation_checkpointing_config
+    from hcache_deepspeed_b200.runtime.zero.test import test1
+    test1()
+    assert iu.is_gated(iu.ActivationType.SiGLU) and not iu.is_gated(iu.ActivationType.GELU)
+    assert iu.native_act_id(iu.ActivationType.GEGLU) == 1 and iu.ceil_div(7, 2) == 4 and iu.elem_size(torch.bfloat16) == 2
+    cfg = tc.get_tensor_parallel_config({"tensor_parallel": {"autotp_size": 2, "tp_grain_size": 64}})
+    assert cfg.autotp_size == 2 and cfg.tensor_parallel.tp_grain_size == 64
+    assert uc.get_timers_config({"timers": {"throughput": {"enabled": False}}}).enabled is False
+    assert get_activation_checkpointing_config({"activation_checkpointing": {"cpu_checkpointing": True}}).cpu_checkpointing
+    assert inference_logger() is inference_logger()
+    torch.manual_seed(0)
+    q = FP_Quantize(group_size=64)
+    w = torch.randn(64, 32, dtype=torch.bfloat16)
+    codes, scales = q.quantize(w, return_meta_tensor=True)
+    x = torch.randn(4, 64, dtype=torch.bfloat16)
+    y = fg.matmul_fp8(x, codes, scales, 64, q)
+    assert y.shape == (4, 32) and (y.float() - x.float() @ w.float()).abs().max() < 1.5
