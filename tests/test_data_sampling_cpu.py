@@ -179,3 +179,26 @@ def test_convert_to_random_ltd_and_clean_state_dict():
     assert any("random_ltd_layer" in k for k in model.state_dict())
     assert list(save_without_random_ltd(model)) == keys
     assert model(torch.randn(2, 3, 4)).shape == (2, 3, 4)
+
+
+def test_data_efficiency_config_tree_and_routing_helpers():
+    import torch
+
+    from hcache_deepspeed_b200.runtime.data_pipeline.config import (get_curriculum_params_legacy, get_data_efficiency_config,
+                                                                    get_random_ltd_enabled)
+    from hcache_deepspeed_b200.runtime.data_pipeline.data_routing.scheduler import BaseScheduler
+    from hcache_deepspeed_b200.runtime.data_pipeline.data_routing.utils import bsh_decoder_gather, bsh_decoder_scatter
+    c = get_data_efficiency_config({"data_efficiency": {"enabled": True, "data_routing": {"enabled": True, "random_ltd": {"enabled": True}}}})
+    assert c["enabled"] and c["seed"] == 1234 and c["data_sampling"]["num_epochs"] == 1000
+    assert c["data_sampling"]["curriculum_learning"]["enabled"] is False and c["data_routing"]["random_ltd"]["enabled"]
+    assert get_random_ltd_enabled({"data_efficiency": {"data_routing": {"random_ltd": {"enabled": True}}}})
+    assert get_curriculum_params_legacy({}) is False
+    assert get_curriculum_params_legacy({"curriculum_learning": {"enabled": True, "min_difficulty": 8}}) == {"min_difficulty": 8}
+    h = torch.randn(2, 10, 4)
+    part, idx, _ = bsh_decoder_gather(6, h, None)
+    assert part.shape == (2, 6, 4) and bool((idx[:, 1:] > idx[:, :-1]).all())
+    out = bsh_decoder_scatter(h, part * 0, idx)
+    assert int((out.abs().sum(-1) == 0).sum()) == 12
+    b = BaseScheduler()
+    b.state = {"schedule_type": "fixed_linear", "min_value": 16, "max_value": 128, "schedule_config": {"require_steps": 100, "seq_per_step": 16}}
+    assert [b.get_value(s) for s in (0, 50, 1000)] == [16, 64, 128]
