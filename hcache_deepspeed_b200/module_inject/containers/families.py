@@ -135,3 +135,28 @@ def distil_bert(block, cfg) -> LayerTensors:
         input_nw=block.output_layer_norm.weight.detach(), input_nb=_b(block.output_layer_norm),
         hidden_size=cfg.dim, heads=cfg.n_heads, eps=1e-12, act=_ACT.get(cfg.activation, "gelu"), pre_layer_norm=False,
         triangular_masking=False)
+
+
+def _llama_like(block, cfg) -> LayerTensors:
+    """Llama / Mistral / Qwen2 / InternLM decoder layers: RMSNorm, rotate-half RoPE over the whole head, grouped KV
+    heads, SiLU-gated MLP (the fused layer wants ``[up | gate]`` columns: ``up * silu(gate)``)."""
+    a, m = block.self_attn, block.mlp
+    h = cfg.num_attention_heads
+    kv = getattr(cfg, "num_key_value_heads", None) or h
+    d = getattr(cfg, "head_dim", None) or cfg.hidden_size // h
+    bias = [x.bias for x in (a.q_proj, a.k_proj, a.v_proj)]
+    qkvb = None if all(b is None for b in bias) else _cat(*[
+        (b.detach() if b is not None else torch.zeros(x.weight.shape[0], dtype=x.weight.dtype, device=x.weight.device))
+        for b, x in zip(bias, (a.q_proj, a.k_proj, a.v_proj))])
+    return LayerTensors(
+        qkvw=_cat(t(a.q_proj.weight), t(a.k_proj.weight), t(a.v_proj.weight)), qkvb=qkvb, ow=t(a.o_proj.weight), ob=_b(a.o_proj),
+        inter_w=_cat(t(m.up_proj.weight), t(m.gate_proj.weight)), inter_b=None, out_w=t(m.down_proj.weight), out_b=_b(m.down_proj),
+        attn_nw=block.post_attention_layernorm.weight.detach(), attn_nb=None,
+        input_nw=block.input_layernorm.weight.detach(), input_nb=None,
+        hidden_size=cfg.hidden_size, heads=h, num_kv=kv, eps=cfg.rms_norm_eps, act="gated_silu", norm_type="rms_norm",
+        rotary_dim=d, rotate_half=True, rope_theta=_rope_theta(cfg))
+
+
+for _cls, _family in (("LlamaDecoderLayer", "llama"), ("MistralDecoderLayer", "mistral"), ("Qwen2DecoderLayer", "qwen2"),
+                      ("InternLMDecoderLayer", "internlm")):
+    register_policy(_cls, _family)(_llama_like)

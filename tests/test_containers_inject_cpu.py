@@ -7,7 +7,7 @@ import torch
 
 transformers = pytest.importorskip("transformers")
 from transformers import (AutoModel, AutoModelForCausalLM, BertConfig, BloomConfig, DistilBertConfig, GPT2Config,  # noqa: E402
-                          GPTJConfig, GPTNeoConfig, GPTNeoXConfig, OPTConfig)
+                          GPTJConfig, GPTNeoConfig, GPTNeoXConfig, LlamaConfig, MistralConfig, OPTConfig, Qwen2Config)
 
 import hcache_deepspeed_b200 as ds  # noqa: E402
 from hcache_deepspeed_b200.module_inject.containers import (POLICIES, InjectedLayer, LayerTensors, build_fused_layer,  # noqa: E402
@@ -25,6 +25,12 @@ CAUSAL = {
     "gptneo": lambda: GPTNeoConfig(hidden_size=32, num_heads=4, num_layers=2, vocab_size=50, attention_types=[[["global"], 2]],
                                    max_position_embeddings=64),
     "bloom": lambda: BloomConfig(hidden_size=32, n_head=4, n_layer=2, vocab_size=50),
+    "llama_gqa": lambda: LlamaConfig(hidden_size=32, num_attention_heads=4, num_key_value_heads=2, num_hidden_layers=2, vocab_size=50,
+                                     intermediate_size=64, max_position_embeddings=64),
+    "qwen2_qkv_bias": lambda: Qwen2Config(hidden_size=32, num_attention_heads=4, num_key_value_heads=2, num_hidden_layers=2,
+                                          vocab_size=50, intermediate_size=64, max_position_embeddings=64),
+    "mistral": lambda: MistralConfig(hidden_size=32, num_attention_heads=4, num_key_value_heads=4, num_hidden_layers=2, vocab_size=50,
+                                     intermediate_size=64, max_position_embeddings=64, sliding_window=None),
 }
 ENCODERS = {
     "bert": lambda: BertConfig(hidden_size=32, num_attention_heads=4, num_hidden_layers=2, vocab_size=50, intermediate_size=64),
