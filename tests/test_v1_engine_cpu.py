@@ -154,3 +154,43 @@ def test_moe_inference_layer_matches_dense_evaluation():
         torch.testing.assert_close(out, res + moe.view_as(res), rtol=1e-4, atol=1e-5)
     y, (kk, vv) = layer(x, use_cache=True)
     assert kk.shape[2] == 6
+
+
+def test_v1_op_binding_objects():
+    import math
+
+    import torch
+
+    from hcache_deepspeed_b200.ops.transformer.inference.config import DeepSpeedInferenceConfig
+    from hcache_deepspeed_b200.ops.transformer.inference.op_binding import (BiasGeluOp, EinsumSecSmEcmOp, GatedActivationOp,
+                                                                           LayerNormOp, LinearOp, MLPGemmOp, QKVGemmOp,
+                                                                           RMSNormOp, SoftmaxContextOp, SoftmaxOp, WorkspaceOp)
+    torch.manual_seed(0)
+    cfg = DeepSpeedInferenceConfig(hidden_size=16, heads=2, intermediate_size=32, num_hidden_layers=1, dtype=torch.float32,
+                                   pre_layer_norm=True, triangular_masking=True, max_out_tokens=32, rotate_every_two=False)
+    x, g, b = torch.randn(2, 5, 16), torch.rand(16) + 0.5, torch.randn(16)
+    torch.testing.assert_close(LayerNormOp(cfg)(x, g, b, 1e-5), torch.nn.functional.layer_norm(x, (16,), g, b, 1e-5))
+    torch.testing.assert_close(RMSNormOp(cfg)(x, g, 1e-6), x * torch.rsqrt(x.pow(2).mean(-1, keepdim=True) + 1e-6) * g)
+    torch.testing.assert_close(BiasGeluOp(cfg)(x, b), torch.nn.functional.gelu(x + b))
+    h = torch.randn(2, 5, 32)
+    a_, g_ = h.chunk(2, -1)
+    torch.testing.assert_close(GatedActivationOp(cfg)(h, None, "silu"), a_ * torch.nn.functional.silu(g_))
+    wqkv, bqkv = torch.randn(16, 48) / 4, torch.randn(48)
+    qkv = QKVGemmOp(cfg)(x, wqkv, bqkv, g, b)
+    qkv = qkv[0] if isinstance(qkv, tuple) else qkv
+    torch.testing.assert_close(qkv, torch.nn.functional.layer_norm(x, (16,), g, b, cfg.layer_norm_eps) @ wqkv + bqkv, atol=1e-5, rtol=1e-5)
+    ctx, kc, vc = SoftmaxContextOp(cfg)(qkv, None, 2, 2, 8 ** -0.25, False, 0, 1, None)   # the factor is applied to q and to k
+    q, k, v = (t.view(2, 5, 2, 8).transpose(1, 2) for t in qkv.split(16, -1))
+    want = torch.nn.functional.scaled_dot_product_attention(q, k, v, is_causal=True).transpose(1, 2).reshape(2, 5, 16)
+    torch.testing.assert_close(ctx, want, atol=1e-5, rtol=1e-5)
+    scores = torch.randn(2, 2, 5, 5)
+    p = SoftmaxOp(cfg)(scores, None, None, True, False, False, 1, False, 1.0, 0)
+    assert torch.allclose(p.sum(-1), torch.ones(2, 2, 5)) and float(p[0, 0, 0, 1:].sum()) == 0.0
+    w = torch.randn(16, 8)
+    torch.testing.assert_close(LinearOp(cfg)(x, w, torch.ones(8), add_bias=True), x @ w + 1)
+    assert EinsumSecSmEcmOp(cfg)(torch.randn(3, 4, 5), torch.randn(3, 6)).shape == (4, 5, 6)
+    out = MLPGemmOp(cfg)(x, x, torch.randn(16, 32) / 4, torch.randn(32, 16) / 4, None, torch.zeros(32), g, b)
+    assert out[0].shape == (2, 5, 16)
+    ws = WorkspaceOp(cfg)
+    ws.reset_cache()
+    assert ws.is_allocated() and ws.retake_workspace()
