@@ -194,3 +194,58 @@ def test_v1_op_binding_objects():
     ws = WorkspaceOp(cfg)
     ws.reset_cache()
     assert ws.is_allocated() and ws.retake_workspace()
+
+
+def test_diffusers_transformer_block_matches_equivalent_module():
+    """A stand-in with the attribute layout of diffusers' BasicTransformerBlock -> the fused block gives the same output."""
+    import torch
+    from torch import nn
+
+    from hcache_deepspeed_b200.ops.transformer.inference import (DeepSpeedDiffusersTransformerBlock,
+                                                                 Diffusers2DTransformerConfig)
+    from hcache_deepspeed_b200.ops.transformer.inference.bias_add import nhwc_bias_add
+    from hcache_deepspeed_b200.ops.transformer.inference.ds_attention import BloomSelfAttention, DeepSpeedSelfAttention
+    assert BloomSelfAttention is DeepSpeedSelfAttention and callable(nhwc_bias_add)
+
+    class Attn(nn.Module):
+        def __init__(self, dim, ctx_dim, heads):
+            super().__init__()
+            self.heads = heads
+            self.to_q, self.to_k, self.to_v = nn.Linear(dim, dim, bias=False), nn.Linear(ctx_dim, dim, bias=False), nn.Linear(ctx_dim, dim, bias=False)
+            self.to_out = nn.ModuleList([nn.Linear(dim, dim), nn.Dropout(0.0)])
+
+        def forward(self, x, context=None):
+            c = x if context is None else context
+            sp = lambda t: t.view(t.shape[0], t.shape[1], self.heads, -1).transpose(1, 2)  # noqa: E731
+            o = torch.nn.functional.scaled_dot_product_attention(sp(self.to_q(x)), sp(self.to_k(c)), sp(self.to_v(c)))
+            return self.to_out[0](o.transpose(1, 2).reshape(x.shape))
+
+    class GEGLU(nn.Module):
+        def __init__(self, dim, inner):
+            super().__init__()
+            self.proj = nn.Linear(dim, 2 * inner)
+
+        def forward(self, x):
+            a, g = self.proj(x).chunk(2, -1)
+            return a * torch.nn.functional.gelu(g)
+
+    class Block(nn.Module):
+        def __init__(self, dim=32, ctx_dim=24, heads=4):
+            super().__init__()
+            self.norm1, self.norm2, self.norm3 = nn.LayerNorm(dim), nn.LayerNorm(dim), nn.LayerNorm(dim)
+            self.attn1, self.attn2 = Attn(dim, dim, heads), Attn(dim, ctx_dim, heads)
+            self.ff = nn.Module()
+            self.ff.net = nn.ModuleList([GEGLU(dim, 64), nn.Dropout(0.0), nn.Linear(64, dim)])
+
+        def forward(self, x, context):
+            x = x + self.attn1(self.norm1(x))
+            x = x + self.attn2(self.norm2(x), context)
+            return x + self.ff.net[2](self.ff.net[0](self.norm3(x)))
+
+    torch.manual_seed(0)
+    blk = Block().eval()
+    x, ctx = torch.randn(2, 10, 32), torch.randn(2, 7, 24)
+    fused = DeepSpeedDiffusersTransformerBlock(blk, Diffusers2DTransformerConfig())
+    with torch.no_grad():
+        torch.testing.assert_close(fused(x, context=ctx), blk(x, ctx), atol=1e-5, rtol=1e-5)
+        torch.testing.assert_close(fused(x, encoder_hidden_states=ctx), blk(x, ctx), atol=1e-5, rtol=1e-5)
