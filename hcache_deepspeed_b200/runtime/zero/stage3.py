@@ -99,8 +99,13 @@ class DeepSpeedZeRoOffload:
         self.trace, self.trace_complete, self.prefetch_plan, self._recording, self._pos = [], False, None, [], 0
 
     def _live_numel(self) -> int:
-        return sum(p.ds_numel for p in self.module.parameters()
-                   if is_zero_param(p) and not p.ds_persist and p.ds_status != ZeroParamStatus.NOT_AVAILABLE)
+        zp = self.__dict__.get("_zero_params")
+        if zp is None:
+            zp = self._zero_params = [p for p in self.module.parameters() if is_zero_param(p)]
+            self._total_numel = sum(p.ds_numel for p in zp)
+        if self.max_live_parameters >= self._total_numel:
+            return 0                # the cap can never bind: skip the scan
+        return sum(p.ds_numel for p in zp if not p.ds_persist and p.ds_status != ZeroParamStatus.NOT_AVAILABLE)
 
     def _derive_plan(self) -> List[List[torch.nn.Parameter]]:
         from ...compile.passes.prefetch import schedule_prefetch

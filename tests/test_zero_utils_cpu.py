@@ -206,3 +206,36 @@ def test_optimizer_swapper_roundtrip(tmp_path, pipelined):
     sw.swap_out_all(masters)
     sw.purge_state()
     assert len(sw._free) == 4
+
+
+@pytest.mark.parametrize("max_live,expect_prefetch", [(10 ** 9, True), (300, False)])
+def test_zero3_trace_prefetch_and_live_cap(max_live, expect_prefetch):
+    """Second iteration on: the next modules' gathers are launched ahead — unless ``max_live_parameters`` forbids it."""
+    from hcache_deepspeed_b200.runtime.zero.stage3 import DeepSpeedZeRoOffload
+    torch.manual_seed(0)
+    ref = torch.nn.Sequential(torch.nn.Linear(16, 16), torch.nn.Tanh(), torch.nn.Linear(16, 16), torch.nn.Tanh(), torch.nn.Linear(16, 4))
+    net = torch.nn.Sequential(torch.nn.Linear(16, 16), torch.nn.Tanh(), torch.nn.Linear(16, 16), torch.nn.Tanh(), torch.nn.Linear(16, 4))
+    net.load_state_dict(ref.state_dict())
+    off = DeepSpeedZeRoOffload(net, prefetch_bucket_size=10 ** 6, max_live_parameters=max_live, param_persistence_threshold=0)
+    grads = {}
+
+    def take(ps):          # what the optimizer's reduce does: consume the gradient
+        for p in ps:
+            grads[id(p)] = p.grad.clone()
+            p.grad = None
+
+    off.reduce_fn = take
+    x = torch.randn(3, 16)
+    for it in range(3):
+        out = net(x)
+        out.sum().backward()
+        assert all(p.numel() == 0 for p in net.parameters())          # everything released again
+    assert off.trace_complete and len(off.trace) == 6 and [ph for _, ph in off.trace] == ["fwd"] * 3 + ["bwd"] * 3
+    assert (off.stats["prefetched"] > 0) == expect_prefetch and off.stats["trace_invalidations"] == 0
+    torch.testing.assert_close(out, ref(x))
+    ref(x).sum().backward()
+    for p, q in zip(net.parameters(), ref.parameters()):
+        torch.testing.assert_close(grads[id(p)], q.grad)
+    # a different module order drops the trace instead of prefetching the wrong parameters
+    net[4](torch.tanh(net[0](x)))
+    assert off.stats["trace_invalidations"] == 1 and not off.trace_complete
