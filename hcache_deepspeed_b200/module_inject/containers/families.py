@@ -160,3 +160,24 @@ def _llama_like(block, cfg) -> LayerTensors:
 for _cls, _family in (("LlamaDecoderLayer", "llama"), ("MistralDecoderLayer", "mistral"), ("Qwen2DecoderLayer", "qwen2"),
                       ("InternLMDecoderLayer", "internlm")):
     register_policy(_cls, _family)(_llama_like)
+
+
+@register_policy("ParallelTransformerLayer", "megatron_gpt")
+def megatron_gpt(block, cfg) -> LayerTensors:
+    """Megatron-LM GPT layer (``containers/megatron_gpt.py`` of the reference): fused ``query_key_value`` stored per head
+    as ``[heads, 3, d]`` (checkpoint version >= 2; ``cfg.megatron_v2=False`` means the older ``[3, heads, d]`` = already
+    ``[q | k | v]``), pre-LN, GELU MLP, learned positions (no rotary in the layer)."""
+    a = getattr(block, "attention", None) or block.self_attention
+    m = block.mlp
+    h = getattr(cfg, "num_attention_heads", None) or cfg.n_head
+    hidden = getattr(cfg, "hidden_size", None) or cfg.n_embd
+    qkvw, qkvb = t(a.query_key_value.weight), _b(a.query_key_value)
+    if getattr(cfg, "megatron_v2", True):
+        qkvw = _per_head_to_qkv(qkvw, h)
+        qkvb = None if qkvb is None else _per_head_to_qkv(qkvb, h)
+    return LayerTensors(
+        qkvw=qkvw, qkvb=qkvb, ow=t(a.dense.weight), ob=_b(a.dense),
+        inter_w=t(m.dense_h_to_4h.weight), inter_b=_b(m.dense_h_to_4h), out_w=t(m.dense_4h_to_h.weight), out_b=_b(m.dense_4h_to_h),
+        attn_nw=block.post_attention_layernorm.weight.detach(), attn_nb=_b(block.post_attention_layernorm),
+        input_nw=block.input_layernorm.weight.detach(), input_nb=_b(block.input_layernorm),
+        hidden_size=hidden, heads=h, eps=getattr(cfg, "layernorm_epsilon", 1e-5), act="gelu")

@@ -153,3 +153,39 @@ def test_checkpoint_json_into_meta_model_then_inject(tmp_path):
     eng2 = ds.init_inference(plain, dtype=torch.float32, checkpoint=str(folder))
     with torch.no_grad():
         torch.testing.assert_close(eng2(ids).logits, want, rtol=1e-4, atol=1e-5)
+
+
+def test_megatron_gpt_policy_against_a_plain_block():
+    """A stand-in with Megatron's ParallelTransformerLayer attribute layout (per-head [h, 3, d] fused QKV)."""
+    from types import SimpleNamespace
+
+    from torch import nn
+    torch.manual_seed(0)
+    H, heads, d = 32, 4, 8
+
+    class ParallelTransformerLayer(nn.Module):
+        def __init__(self):
+            super().__init__()
+            self.input_layernorm, self.post_attention_layernorm = nn.LayerNorm(H), nn.LayerNorm(H)
+            self.attention = nn.Module()
+            self.attention.query_key_value, self.attention.dense = nn.Linear(H, 3 * H), nn.Linear(H, H)
+            self.mlp = nn.Module()
+            self.mlp.dense_h_to_4h, self.mlp.dense_4h_to_h = nn.Linear(H, 4 * H), nn.Linear(4 * H, H)
+
+        def forward(self, x):
+            b, s, _ = x.shape
+            qkv = self.attention.query_key_value(self.input_layernorm(x)).view(b, s, heads, 3, d)
+            q, k, v = (qkv[:, :, :, i].transpose(1, 2) for i in range(3))
+            ctx = torch.nn.functional.scaled_dot_product_attention(q, k, v, is_causal=True).transpose(1, 2).reshape(b, s, H)
+            x = x + self.attention.dense(ctx)
+            return x + self.mlp.dense_4h_to_h(torch.nn.functional.gelu(self.mlp.dense_h_to_4h(self.post_attention_layernorm(x))))
+
+    block = ParallelTransformerLayer().eval()
+    cfg = SimpleNamespace(hidden_size=H, num_attention_heads=heads, layernorm_epsilon=1e-5)
+    lt = POLICIES["ParallelTransformerLayer"](block, cfg)
+    fused = build_fused_layer(lt, 1, torch.float32)
+    x = torch.randn(2, 6, H)
+    with torch.no_grad():
+        got = fused(x)
+        got = got[0] if isinstance(got, tuple) else got
+        torch.testing.assert_close(got, block(x), atol=1e-5, rtol=1e-5)
