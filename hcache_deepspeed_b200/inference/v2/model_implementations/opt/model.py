@@ -1,0 +1,7 @@
+"""Model class of the ``opt`` family. The reference has one hand-written forward per family; here every family runs
+on the one ragged executor, parameterised by the family's ``ArchSpec`` (``models/families.py``)."""
+from .....models.transformer import RaggedTransformer
+
+
+class OPTInferenceModel(RaggedTransformer):
+    model_type = "opt"
