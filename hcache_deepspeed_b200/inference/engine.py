@@ -287,10 +287,9 @@ class InferenceEngine(torch.nn.Module):
             for _ in range(3):
                 self.module(*inputs, **kwargs)
         torch.cuda.current_stream().wait_stream(side)
-        self._cuda_graph = torch.cuda.CUDAGraph()
+        from ..utils.cuda_graph import capture
         self._graph_inputs, self._graph_kwargs = inputs, kwargs
-        with torch.cuda.graph(self._cuda_graph):
-            self._graph_output = self.module(*self._graph_inputs, **self._graph_kwargs)
+        self._cuda_graph, self._graph_output = capture(lambda: self.module(*self._graph_inputs, **self._graph_kwargs))
         self._cuda_graph.replay()
         return self._graph_output
 

@@ -259,19 +259,22 @@ class InferenceEngineV2:
             self._decode_warm[key] = seen + 1
             if seen < 2:  # first steps run eagerly (lazy kernel attribute setup, allocator warm-up)
                 return model.forward(batch, capture=False)[0]
-            torch.cuda.synchronize(model.device)
-            graph = torch.cuda.CUDAGraph()
-            side = torch.cuda.Stream(device=model.device)
-            side.wait_stream(torch.cuda.current_stream())
             from ...ops import kernels as _k
+            from ...utils.cuda_graph import capture
             before = _k.launch_count
-            with torch.cuda.stream(side):
-                with torch.cuda.graph(graph, stream=side):
-                    static_logits = model.forward(batch, capture=False)[0]
-            torch.cuda.current_stream().wait_stream(side)
+            try:
+                graph, static_logits = capture(lambda: model.forward(batch, capture=False)[0], device=model.device)
+            except Exception as e:  # keep serving eagerly; a failed capture launched nothing
+                _k.launch_count = before
+                inference_logger().warning(f"CUDA-graph capture of the decode step failed ({type(e).__name__}: {e}); "
+                                           f"batch shape {key} stays on the eager path")
+                self._decode_graphs[key] = entry = (None, None, 0)
+                return model.forward(batch, capture=False)[0]
             entry = (graph, static_logits, _k.launch_count - before)
             _k.launch_count = before  # capture launched nothing; replays account for the kernels they run
             self._decode_graphs[key] = entry
+        if entry[0] is None:
+            return model.forward(batch, capture=False)[0]
         entry[0].replay()
         from ...ops import kernels as _k
         _k.launch_count += entry[2]

@@ -53,9 +53,8 @@ class GraphedCallable:
             for _ in range(self.warmup):
                 self.fn(*s_args, **s_kwargs)
         torch.cuda.current_stream().wait_stream(side)
-        graph = torch.cuda.CUDAGraph()
-        with torch.cuda.graph(graph):
-            out = self.fn(*s_args, **s_kwargs)
+        from ...utils.cuda_graph import capture
+        graph, out = capture(lambda: self.fn(*s_args, **s_kwargs))
         self._graphs[key] = (graph, s_args, s_kwargs, out)
 
     def __call__(self, *args, **kwargs):

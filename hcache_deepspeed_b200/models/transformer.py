@@ -19,6 +19,7 @@ Plays the role of the reference's ``DSTransformerModelBase`` + per-family ``mode
 """
 from __future__ import annotations
 
+import os
 from typing import List, Optional, Sequence, Tuple
 
 import torch
@@ -37,6 +38,10 @@ ACCUM_MAX_TOKENS = 256
 FP8_ACCUM_MAX_TOKENS = 64   # fp8 weights: the fp32-accumulate epilogue exists on the decode (feature-major) kernel only
 #: staging slots of the restore pipeline (H2D of layer l+1.. overlaps the projection of layer l)
 RESTORE_SLOTS = 4
+#: tensor parallel: up to this many tokens the collective after a row-parallel GEMM is a one-shot all-reduce inside the
+#: norm kernel (one flag exchange, every rank reduces every row); above it reduce-scatter + all-gather (each rank reduces
+#: only its rows: tp x fewer NVLink bytes, one more flag exchange)
+TP_ONESHOT_MAX_TOKENS = int(os.environ.get("HDS_TP_ONESHOT_TOKENS", "16"))
 
 
 def ceil_div(a: int, b: int) -> int:
@@ -151,17 +156,24 @@ class RaggedTransformer:
         inter = max(self.info.inter, self.info.moe_inter_range[1] - self.info.moe_inter_range[0],
                     self.info.shared_inter_range[1] - self.info.shared_inter_range[0])
         qkv_cols = (self.n_q + 2 * self.n_kv) * self.d
+        self._tp_fused = self.tp_size > 1 and bool(getattr(self.comm, "fused", False))
+        self._tp_wait_next = False   # the latest norm output was all-gathered by the peers: its first reader must wait
+        #: reduce-scatter + all-gather norms need every rank to write into every rank's activation buffers
+        self._tp_scatter_ok = self._tp_fused and not s.is_moe and not s.parallel_residual and s.final_norm
+        sym = (lambda *shape, dtype=dt: self.comm.alloc_symmetric(shape, dtype)) if self._tp_scatter_ok else buf
         self.residual = buf(T, H)
-        self.xn = buf(T, H)
-        self.xn2 = buf(T, H)
-        self.latent_buf = buf(s.n_layers, T, H) if self.capture_enabled else None
+        self.xn = sym(T, H)
+        self.xn2 = sym(T, H)
+        self.latent_buf = sym(s.n_layers, T, H) if self.capture_enabled else None
+        #: 16-bit partial sums of the store-epilogue (prefill-size) row-parallel GEMMs, reduced by the next norm kernel
+        self.partial16 = self.comm.alloc_symmetric((T, H), dt) if self._tp_fused else None
         self.qkv_buf = buf(T, qkv_cols)
         self.q_buf = buf(T, self.n_q * self.d)
         self.attn_buf = buf(T, self.n_q * self.d)
         self.act_buf = buf(T, inter)
         # fp32 pending-delta buffers; two alternate under tensor parallelism (symmetric memory when fused) so a
         # fast rank's next reducing GEMM never lands in a buffer a slow rank is still consuming
-        if self.tp_size > 1 and getattr(self.comm, "fused", False):
+        if self._tp_fused:
             self._delta_bufs = self.comm.alloc_delta(T, H, 2)
         else:
             self._delta_bufs = [buf(T, H, dtype=torch.float32) for _ in range(2 if self.tp_size > 1 else 1)]
@@ -169,7 +181,7 @@ class RaggedTransformer:
         self.delta32 = self._delta_bufs[0]
         self.delta16 = buf(T, H)
         self.hidden_last = buf(S, H)
-        self.logits_local = buf(S, self.info.vocab)
+        self.logits_local = self.comm.alloc_symmetric((S, self.info.vocab), dt) if self._tp_fused else buf(S, self.info.vocab)
         self.logits_full = buf(S, s.vocab) if self.tp_size > 1 else None
         self.kv_scratch = None
         self.ws_gemm = self.ws_small = self.ws_large = None
@@ -264,9 +276,10 @@ class RaggedTransformer:
         """``quantization_mode = "wf8af8"``: convert every layer's QKV / attention-out / MLP weights to E4M3 with
         per-output-channel scales (embedding, LM head and norms stay 16-bit). Returns the bytes saved."""
         s = self.spec
-        if self.tp_size > 1 or s.is_moe or s.parallel_residual:
-            raise NotImplementedError("wf8af8 covers dense, sequential-residual models on one GPU (tensor-parallel, "
-                                      "mixture-of-experts and parallel-residual blocks reduce through fp32 partial sums)")
+        if s.is_moe or s.parallel_residual or (self.tp_size > 1 and not self._tp_fused):
+            raise NotImplementedError("wf8af8 covers dense, sequential-residual models (tensor parallel: with the fused "
+                                      "flag-protocol collectives; mixture-of-experts and parallel-residual blocks reduce "
+                                      "through fp32 partial sums)")
         saved = 0
         for lw in self.w.layers:
             for name in ("w_qkv", "w_o", "w_up", "w_down"):
@@ -285,35 +298,60 @@ class RaggedTransformer:
     # ------------------------------------------------------------------------------------------------
     # forward
     # ------------------------------------------------------------------------------------------------
+    def _tp_scatter(self, T: int) -> bool:
+        """Shape of the collective inside the norm kernels of a T-token forward (see TP_ONESHOT_MAX_TOKENS)."""
+        return self._tp_scatter_ok and T > TP_ONESHOT_MAX_TOKENS
+
+    def _tp_rows(self, T: int) -> Tuple[int, int]:
+        """(first row, row count) of the residual stream this rank owns under reduce-scatter + all-gather."""
+        per = ceil_div(T, self.tp_size)
+        r0 = min(T, self.tp_rank * per)
+        return r0, min(T, r0 + per) - r0
+
     def _norm(self, x, gamma, out, beta=None, delta=None, res_out=None) -> torch.Tensor:
-        """Norm that folds the pending delta into the residual stream. Under fused (pull) tensor parallelism the fp32
-        delta is the sum of every rank's buffer, read over NVLink inside the kernel, and the other buffer of the
-        alternating pair is cleared for the next reducing GEMM."""
+        """Norm that folds the pending delta into the residual stream. Under fused tensor parallelism the delta is this
+        rank's partial-sum buffer and the kernel performs the collective over NVLink (``hds_norm_tp``): one-shot
+        all-reduce for small batches, reduce-scatter + all-gather (``out`` written on every rank, flag signalled, first
+        reader must wait) otherwise. fp32 partial sums alternate between two buffers; the idle one is cleared here."""
         s = self.spec
-        zero_buf = None
-        comm = None
-        if (delta is not None and delta.dtype == torch.float32 and self.tp_size > 1 and getattr(self.comm, "fused", False)
-                and self.comm.mode == "pull"):
-            comm = self.comm
-            i = 0 if delta.data_ptr() == self._delta_bufs[0].data_ptr() else 1
-            zero_buf = self._delta_bufs[1 - i][:delta.shape[0]]
-        return self.ops.norm(x, gamma, out, beta=beta, delta=delta, zero_delta=comm is None, res_out=res_out,
-                             eps=s.norm_eps, layer_norm=s.norm == "layer", comm=comm, zero_buf=zero_buf)
+        if delta is not None and self._tp_fused:
+            T = delta.shape[0]
+            zero_buf = None
+            if delta.dtype == torch.float32:
+                i = 0 if delta.data_ptr() == self._delta_bufs[0].data_ptr() else 1
+                zero_buf = self._delta_bufs[1 - i][:T]
+            scatter = None
+            if self._tp_scatter(T):
+                scatter = self._tp_rows(T)
+                self._tp_wait_next = True
+            return self.ops.norm(x, gamma, out, beta=beta, delta=delta, res_out=res_out, eps=s.norm_eps,
+                                 layer_norm=s.norm == "layer", comm=self.comm, zero_buf=zero_buf, scatter_rows=scatter)
+        return self.ops.norm(x, gamma, out, beta=beta, delta=delta, zero_delta=True, res_out=res_out, eps=s.norm_eps,
+                             layer_norm=s.norm == "layer")
+
+    def _take_tp_wait(self) -> bool:
+        """True once after a reduce-scatter + all-gather norm: the caller passes it to the first reader of that output."""
+        w, self._tp_wait_next = self._tp_wait_next, False
+        return w
 
     def _row_parallel(self, x: torch.Tensor, w: torch.Tensor, b: Optional[torch.Tensor], T: int, force_accum: bool,
                       last_into_delta: bool = True) -> torch.Tensor:
-        """y = x @ w.T (+b), left as the pending delta. fp32 partial sums when the GEMM is split over K or ranks."""
-        if isinstance(w, Fp8Weight) and T > FP8_ACCUM_MAX_TOKENS:
-            return self.ops.gemm(x, w, self.delta16[:T], bias=b)   # W8A8 prefill: scaled store epilogue, 16-bit delta
-        if force_accum or T <= ACCUM_MAX_TOKENS or self.tp_size > 1:
-            d32 = self._delta_bufs[self._delta_idx][:T]
-            self.ops.gemm_accum(x, w, d32, bias=b, comm=self.comm)
-            if last_into_delta:  # this delta is complete: the next reducing GEMM uses the other buffer
-                if self.tp_size > 1:
-                    self.comm.all_reduce_delta(d32)
-                self._delta_idx = (self._delta_idx + 1) % len(self._delta_bufs)
-            return d32
-        return self.ops.gemm(x, w, self.delta16[:T], bias=b)
+        """y = x @ w.T (+b), left as the pending delta: fp32 partial sums when the GEMM is split over K (decode-size
+        batches, parallel-residual blocks), else a 16-bit store. Tensor parallel (fused): the buffers are symmetric
+        memory, the GEMM's last CTA signals the peers, the next norm kernel reduces over the ranks."""
+        tp = self._tp_fused
+        fp8 = isinstance(w, Fp8Weight)
+        accum = force_accum or T <= (FP8_ACCUM_MAX_TOKENS if fp8 else ACCUM_MAX_TOKENS) or (self.tp_size > 1 and not tp)
+        if not accum:
+            out16 = self.partial16[:T] if tp else self.delta16[:T]
+            return self.ops.gemm(x, w, out16, bias=b, comm=self.comm, tp_signal=tp)
+        d32 = self._delta_bufs[self._delta_idx][:T]
+        self.ops.gemm_accum(x, w, d32, bias=b, comm=self.comm, tp_signal=tp and last_into_delta)
+        if last_into_delta:  # this delta is complete: the next reducing GEMM uses the other buffer
+            if self.tp_size > 1 and not tp:
+                self.comm.all_reduce_delta(d32)
+            self._delta_idx = (self._delta_idx + 1) % len(self._delta_bufs)
+        return d32
 
     def _mlp(self, x: torch.Tensor, lw, T: int, force_accum: bool) -> torch.Tensor:
         s = self.spec
@@ -321,7 +359,8 @@ class RaggedTransformer:
             return self._moe(x, lw, T)
         n_act = lw.w_up.shape[0] // (2 if s.gated_mlp else 1)
         act = self.act_buf[:T, :n_act]
-        self.ops.gemm(x, lw.w_up, act, bias=lw.b_up, act=self.act, gated=s.gated_mlp, workspace=self.ws_gemm)
+        self.ops.gemm(x, lw.w_up, act, bias=lw.b_up, act=self.act, gated=s.gated_mlp, workspace=self.ws_gemm,
+                      comm=self.comm, tp_wait=self._take_tp_wait())
         return self._row_parallel(act, lw.w_down, lw.b_down, T, force_accum)
 
     def _moe_state(self, lw, E: int, kk: int) -> dict:
@@ -399,11 +438,10 @@ class RaggedTransformer:
             g = torch.sigmoid(ref.gemm(x, lw.w_shared_gate, out_dtype=torch.float32))
             d32 += ys.float() * g
         if self.tp_size > 1:
-            if getattr(self.comm, "fused", False) and self.comm.mode == "push":
-                import torch.distributed as dist
-                dist.all_reduce(d32, group=self.comm.group)  # MoE partials were added locally: plain all-reduce
+            if self._tp_fused:
+                self.comm.signal()               # partial sums complete on this rank: the next norm kernel reduces them
             else:
-                self.comm.all_reduce_delta(d32)  # NCCL all-reduce, or (pull mode) just the barrier
+                self.comm.all_reduce_delta(d32)  # NCCL all-reduce
         self._delta_idx = (self._delta_idx + 1) % len(self._delta_bufs)
         return d32
 
@@ -441,7 +479,8 @@ class RaggedTransformer:
             if self._pending_restore is not None:
                 self._restore_step(li)  # deferred HCache restore: this layer's K/V must land before its attention
             ops.qkv_rope_kv_append(xn, lw.w_qkv, lw.b_qkv, self.qkv_buf[:T], self.q_buf[:T], kv_layer, pos, slot,
-                                   self.inv_freq, self.n_q, self.n_kv, self.d, s.rot_dim, bs, workspace=self.ws_gemm)
+                                   self.inv_freq, self.n_q, self.n_kv, self.d, s.rot_dim, bs, workspace=self.ws_gemm,
+                                   comm=self.comm, tp_wait=self._take_tp_wait())
             attn = self.attn_buf[:T]
             ops.attention(self.q_buf[:T], attn, kv_layer, batch, self.n_q, self.n_kv, self.d, self.scale,
                           ws_small=self.ws_small, ws_large=self.ws_large)
@@ -463,6 +502,8 @@ class RaggedTransformer:
                 if st["done"] >= len(st["layers"]):
                     self._pending_restore = None
         if n_layers_limit is not None:
+            if self._take_tp_wait():
+                self.comm.wait()
             if pending is not None and pending.dtype == torch.float32:
                 # the partial sums of the last executed layer are not consumed by a norm; under pull-mode TP the
                 # previously consumed buffer is still dirty as well (every rank is past the barrier that follows
@@ -477,21 +518,37 @@ class RaggedTransformer:
         if s.final_norm:
             self._norm(resid, w.final_norm_g, fin, beta=w.final_norm_b, delta=pending)
         else:
+            # no final norm: only the residual add (and, tensor parallel, the reduction) is wanted -> res_out; `fin` must hold
+            # every row on every rank, so this one always takes the all-reduce shape
             ones = torch.ones(s.hidden, dtype=self.dtype, device=self.device)
-            ops.norm(resid, ones, self.xn[:T], delta=pending, zero_delta=True, res_out=fin, eps=s.norm_eps)
+            if pending is not None and self._tp_fused:
+                zb = None
+                if pending.dtype == torch.float32:
+                    i = 0 if pending.data_ptr() == self._delta_bufs[0].data_ptr() else 1
+                    zb = self._delta_bufs[1 - i][:T]
+                ops.norm(resid, ones, self.xn[:T], delta=pending, res_out=fin, eps=s.norm_eps, comm=self.comm, zero_buf=zb)
+            else:
+                ops.norm(resid, ones, self.xn[:T], delta=pending, zero_delta=True, res_out=fin, eps=s.norm_eps)
+        if self._take_tp_wait():
+            self.comm.wait()   # the peers' rows of `fin` have landed
         if all_logits:
             out_local = torch.empty((T, self.info.vocab), dtype=self.dtype, device=self.device)
             logits = ops.gemm(fin, w.lm_head, out_local, bias=w.lm_head_b, workspace=self.ws_gemm)
             n_rows = T
         else:
             hidden = ops.gather_rows(fin, batch.last_rows(), self.hidden_last[:S])
-            logits = ops.gemm(hidden, w.lm_head, self.logits_local[:S], bias=w.lm_head_b, workspace=self.ws_gemm)
+            logits = ops.gemm(hidden, w.lm_head, self.logits_local[:S], bias=w.lm_head_b, workspace=self.ws_gemm,
+                              comm=self.comm, tp_signal=self._tp_fused)
             n_rows = S
         if self.tp_size > 1:
             ranges = [shard_info(s, r, self.tp_size).vocab_range for r in range(self.tp_size)]
-            full = self.logits_full[:S] if not all_logits else torch.empty((n_rows, s.vocab), dtype=self.dtype,
-                                                                           device=self.device)
-            logits = self.comm.all_gather_logits(logits, full, ranges)
+            if self._tp_fused and not all_logits:
+                # vocabulary shards land straight in the final [S, vocab] layout: one pull kernel behind the GEMMs' flags
+                logits = self.comm.gather_logits(logits, self.logits_full[:S], ranges)
+            else:
+                full = self.logits_full[:S] if not all_logits else torch.empty((n_rows, s.vocab), dtype=self.dtype,
+                                                                               device=self.device)
+                logits = self.comm.all_gather_logits(logits, full, ranges)
         return logits, (self.latent_buf[:, :T] if capture else None)
 
     # ------------------------------------------------------------------------------------------------
@@ -583,29 +640,42 @@ class RaggedTransformer:
         comp.wait_event(self.ev_loaded[k])
         wk, bk = self.kv_weight(li)
         if st["sharded"]:
-            # every rank's slice of this layer has landed in its own HBM -> gather inside the projection kernel
+            # My slice of this layer has landed in my HBM (the stream waited for the copy): tell the peers, then gather
+            # every peer's rows over NVLink behind their flags. Slot reuse needs no second exchange: a peer issues the
+            # "landed" signal of layer i+1 only after its gather of layer i, so once MY gather of layer i+1 has passed its
+            # wait every rank is done reading slot k(i) — the copy into that slot waits for an event recorded there.
             _, _, per = shard_rows(T, self.tp_size, self.tp_rank)
-            self.comm.barrier()
+            comm = self.comm
+            comm.signal()
             if self.tp_gather == "copy":
                 # pull every peer's rows once over NVLink into my full-size slot, then project locally
                 slot_t = self.restore_stage_sym[k]
                 if k not in self._slot_peer_ptrs:
-                    self._slot_peer_ptrs[k] = self.comm.peer_ptrs_raw(slot_t)
+                    self._slot_peer_ptrs[k] = comm.peer_ptrs_raw(slot_t)
+                comm.arm(wait=True)
                 self.ops.k.p2p_gather_rows(slot_t, self._slot_peer_ptrs[k], per, T, self.tp_rank)
-                self.comm.barrier()  # peers have read my rows: the slot may be refilled once my kernel is done
+                if i >= 1:
+                    self.ev_consumed[(i - 1) % RESTORE_SLOTS].record(comp)
                 self.ops.restore_kv_proj(slot_t[:T], wk, bk, kv.get_cache(li), self.restore_pos[:T], self.restore_slot[:T],
                                          self.inv_freq, self.n_kv, self.d, s.rot_dim, kv.kv_block_size,
                                          scratch=self.kv_scratch[:T] if self.kv_scratch is not None else None)
             else:
-                ptrs = self.comm.peer_ptrs_raw(self.restore_stage_sym, byte_offset=k * self._sym_rows * s.hidden * 2)
+                comm.wait()
+                if i >= 1:
+                    self.ev_consumed[(i - 1) % RESTORE_SLOTS].record(comp)
+                ptrs = comm.peer_ptrs_raw(self.restore_stage_sym, byte_offset=k * self._sym_rows * s.hidden * 2)
                 self.ops.k.restore_kv_proj_peers(ptrs, per, T, s.hidden, self.dtype, wk, kv.get_cache(li),
                                                  self.restore_pos[:T], self.restore_slot[:T], self.inv_freq, self.n_kv,
                                                  self.d, kv.kv_block_size, bias_kv=bk)
-                self.comm.barrier()  # peers are done reading my slot before it is refilled
-        else:
-            self.ops.restore_kv_proj(self.restore_stage[k][:T], wk, bk, kv.get_cache(li), self.restore_pos[:T],
-                                     self.restore_slot[:T], self.inv_freq, self.n_kv, self.d, s.rot_dim, kv.kv_block_size,
-                                     scratch=self.kv_scratch[:T] if self.kv_scratch is not None else None)
+            st["done"] = i + 1
+            if st["done"] >= len(st["layers"]):
+                comm.barrier()   # every rank has finished reading every slot before the next restore refills them
+            elif i >= 1 and st["issued"] < len(st["layers"]):
+                self._restore_issue_h2d(st)
+            return
+        self.ops.restore_kv_proj(self.restore_stage[k][:T], wk, bk, kv.get_cache(li), self.restore_pos[:T],
+                                 self.restore_slot[:T], self.inv_freq, self.n_kv, self.d, s.rot_dim, kv.kv_block_size,
+                                 scratch=self.kv_scratch[:T] if self.kv_scratch is not None else None)
         self.ev_consumed[k].record(comp)
         st["done"] = i + 1
         if st["issued"] < len(st["layers"]):

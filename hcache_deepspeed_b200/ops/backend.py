@@ -30,12 +30,12 @@ class CpuOps:
     name = "cpu-reference"
 
     # ---- linear ---------------------------------------------------------------------------------
-    def gemm(self, a, w, out, bias=None, act=0, gated=False, workspace=None):
+    def gemm(self, a, w, out, bias=None, act=0, gated=False, workspace=None, comm=None, tp_wait=False, tp_signal=False):
         a, w = _fp8_emulate(a, w)
         out.copy_(ref.gemm(a, w, bias=bias, act=act, gated=gated, out_dtype=out.dtype))
         return out
 
-    def gemm_accum(self, a, w, accum, bias=None, comm=None):
+    def gemm_accum(self, a, w, accum, bias=None, comm=None, tp_signal=False):
         a, w = _fp8_emulate(a, w)
         accum += ref.gemm(a, w, bias=bias, out_dtype=torch.float32)
 
@@ -44,7 +44,7 @@ class CpuOps:
 
     # ---- norm -----------------------------------------------------------------------------------
     def norm(self, x, gamma, out, beta=None, delta=None, zero_delta=False, res_out=None, eps=1e-5, layer_norm=False,
-             comm=None, zero_buf=None):
+             comm=None, zero_buf=None, scatter_rows=None):
         if delta is not None:
             s = (x.float() + delta.float()).to(x.dtype)
             if zero_delta and delta.dtype == torch.float32:
@@ -57,7 +57,7 @@ class CpuOps:
 
     # ---- attention-side -------------------------------------------------------------------------------
     def qkv_rope_kv_append(self, x, w_qkv, b_qkv, qkv_buf, q_out, kv_layer, tok_pos, tok_slot, inv_freq, n_q, n_kv, d,
-                           rot_dim, block_size, workspace=None):
+                           rot_dim, block_size, workspace=None, comm=None, tp_wait=False):
         T = x.shape[0]
         dt = x.dtype
         x, w_qkv = _fp8_emulate(x, w_qkv)
@@ -131,48 +131,71 @@ class CudaOps:
             bufs[K] = (torch.empty(max_tokens, K, dtype=torch.uint8, device=device),
                        torch.empty(max_tokens, dtype=torch.float32, device=device))
 
-    def gemm(self, a, w, out, bias=None, act=0, gated=False, workspace=None):
+    def gemm(self, a, w, out, bias=None, act=0, gated=False, workspace=None, comm=None, tp_wait=False, tp_signal=False):
+        """``tp_wait``: ``a`` was all-gathered into this GPU's buffer by the peers' norm kernels — the first kernel that
+        reads it acquires their flags. ``tp_signal``: the GEMM's last CTA releases ``out`` to the peers."""
         if isinstance(w, Fp8Weight):
+            if tp_wait:
+                comm.arm(wait=True)          # consumed by the activation quantiser, the first reader of `a`
             aq, a_s = self._fp8_act(a)
+            if tp_signal:
+                comm.arm(signal=True)
             return self.k.gemm_fp8(aq, a_s, w.q, w.scale, out, bias=bias, act=act, gated=gated,
                                    workspace=workspace if a.shape[0] <= 64 else None)
+        if tp_wait or tp_signal:
+            comm.arm(wait=tp_wait, signal=tp_signal)
         return self.k.gemm(a, w, bias=bias, act=act, gated=gated, out=out,
                            workspace=workspace if a.shape[0] <= 128 else None)
 
-    def gemm_accum(self, a, w, accum, bias=None, comm=None):
+    def gemm_accum(self, a, w, accum, bias=None, comm=None, tp_signal=False):
+        """``accum (fp32) += a @ w.T``. ``tp_signal`` (tensor parallel): the kernel's last CTA releases the partial sums
+        to the peers; the reduction itself happens in ``norm_tp``."""
         if isinstance(w, Fp8Weight):
-            if a.shape[0] > 64 or (comm is not None and getattr(comm, "size", 1) > 1):
+            if a.shape[0] > 64:
                 raise NotImplementedError("fp8 weights: above 64 tokens the executor routes reducing GEMMs through the "
-                                          "16-bit delta; tensor-parallel reductions are not covered")
+                                          "16-bit partial-sum buffer")
             aq, a_s = self._fp8_act(a)
+            if tp_signal:
+                comm.arm(signal=True)
             self.k.gemm_fp8_accum(aq, a_s, w.q, w.scale, accum, bias=bias, out_dtype=a.dtype)
             return
-        if comm is not None and comm.fused and comm.mode == "push":
-            # GEMM -> all-reduce in the epilogue: reduce the tile into every rank's buffer (NVLS multicast / P2P red)
-            self.k.gemm_accum(a, w, accum, bias=bias, peer_ptrs=comm.peer_ptrs(accum), multicast_ptr=comm.multicast_ptr(accum))
-        else:
-            self.k.gemm_accum(a, w, accum, bias=bias)
+        if tp_signal:
+            comm.arm(signal=True)
+        self.k.gemm_accum(a, w, accum, bias=bias)
 
     def norm(self, x, gamma, out, beta=None, delta=None, zero_delta=False, res_out=None, eps=1e-5, layer_norm=False,
-             comm=None, zero_buf=None):
-        if comm is not None and comm.fused and comm.mode == "pull" and delta is not None and delta.dtype == torch.float32:
-            # pull all-reduce fused into the norm: sum every rank's partial-sum buffer over NVLink
-            return self.k.norm_tp(x, gamma, out, comm.peer_ptrs_raw(delta), zero_buf=zero_buf, beta=beta, res_out=res_out,
-                                  eps=eps, layer_norm=layer_norm)
+             comm=None, zero_buf=None, scatter_rows=None):
+        """``comm`` set: ``delta`` is this rank's partial-sum buffer of a row-parallel GEMM (fp32 or 16-bit, symmetric
+        memory) and the kernel performs the collective (see ``hds_norm_tp``). ``scatter_rows = (row0, n_rows)`` selects
+        the reduce-scatter + all-gather shape: ``out`` (symmetric) is written on every rank and the kernel signals."""
+        if comm is not None and delta is not None:
+            comm.pre_wait()
+            kw = {}
+            if scatter_rows is not None:
+                mc = comm.multicast_ptr(out)
+                kw = dict(row0=scatter_rows[0], n_rows=scatter_rows[1], signal=True, out_mc=mc,
+                          out_ptrs=None if mc else comm.peer_ptrs_raw(out))
+            return self.k.norm_tp(comm.ctx, x, gamma, out, comm.peer_ptrs_raw(delta), src_mc=comm.multicast_ptr(delta),
+                                  partial_16bit=delta.dtype != torch.float32, zero_buf=zero_buf, beta=beta, res_out=res_out,
+                                  eps=eps, layer_norm=layer_norm, **kw)
         return self.k.norm(x, gamma, out, beta=beta, delta=delta, zero_delta=zero_delta, res_out=res_out, eps=eps,
                            layer_norm=layer_norm)
 
     def qkv_rope_kv_append(self, x, w_qkv, b_qkv, qkv_buf, q_out, kv_layer, tok_pos, tok_slot, inv_freq, n_q, n_kv, d,
-                           rot_dim, block_size, workspace=None):
+                           rot_dim, block_size, workspace=None, comm=None, tp_wait=False):
         T = x.shape[0]
         fusable = d in (64, 128) and (inv_freq is None or rot_dim == d)
         if isinstance(w_qkv, Fp8Weight):
-            self.gemm(x, w_qkv, qkv_buf, bias=b_qkv)
+            self.gemm(x, w_qkv, qkv_buf, bias=b_qkv, comm=comm, tp_wait=tp_wait)
             self.k.rope_kv_append(qkv_buf, q_out, kv_layer, tok_pos, tok_slot, inv_freq, n_q, n_kv, d, rot_dim, block_size)
         elif fusable and T >= self.FUSED_QKV_MIN_TOKENS:
+            if tp_wait:
+                comm.arm(wait=True)
             self.k.qkv_rope_proj(x, w_qkv, q_out, kv_layer, tok_pos, tok_slot, inv_freq, n_q, n_kv, d, block_size,
                                  bias_qkv=b_qkv)
         else:
+            if tp_wait:
+                comm.arm(wait=True)
             self.k.gemm(x, w_qkv, bias=b_qkv, out=qkv_buf, workspace=workspace if T <= 128 else None)
             self.k.rope_kv_append(qkv_buf, q_out, kv_layer, tok_pos, tok_slot, inv_freq, n_q, n_kv, d, rot_dim, block_size)
 

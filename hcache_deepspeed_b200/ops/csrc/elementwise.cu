@@ -8,6 +8,7 @@
 //   ragged_ops/logits_gather/logits_gather_cuda.cu:18-50  (all under deepspeed/inference/v2/kernels/).
 #include "hds_ptx.cuh"
 #include "hds_host.cuh"
+#include "tp_sync_host.cuh"
 #include "../../../include/hds_b200.h"
 
 namespace hds {
@@ -32,20 +33,11 @@ __device__ __forceinline__ float block_sum_256(float v, float* red) {
 //               are cleared after being read so the next accumulating GEMM starts from zero.
 //   res_out   : optional, receives x_in + delta (pre-norm) or the normalised value (post_norm)
 //   out       : normalised output;  row_idx: optional gather of input rows (last-token gather)
-// Tensor-parallel pull reduction: the fp32 partial sums of a row-parallel GEMM stay in each rank's own buffer
-// (symmetric memory); the consuming norm kernel adds up all ranks' copies with plain loads over NVLink — no remote
-// atomics, no NCCL kernel — and clears the OTHER buffer of the alternating pair for the next reducing GEMM.
-struct DeltaPeers {
-    const float* src[8];  // same buffer on every rank (this rank's mapping of each), src[0..n)
-    int n;                // 0 = single local delta (the `delta` argument)
-    float* zero_buf;      // local buffer to clear (rows x cols fp32), may be null
-};
-
 template <int VPT, bool kBf16, bool kLayerNorm, bool kDeltaF32>
 __global__ void __launch_bounds__(kNormThreads)
 norm_kernel(const void* __restrict__ x_in, void* delta, void* res_out, void* __restrict__ out,
             const void* __restrict__ gamma, const void* __restrict__ beta, const int32_t* __restrict__ row_idx,
-            int cols, float eps, int zero_delta, int post_norm, int64_t ld_in, int64_t ld_out, const DeltaPeers peers) {
+            int cols, float eps, int zero_delta, int post_norm, int64_t ld_in, int64_t ld_out) {
     __shared__ float red[kNormThreads / 32];
     pdl_enter();
     const int r_out = blockIdx.x;
@@ -63,26 +55,7 @@ norm_kernel(const void* __restrict__ x_in, void* delta, void* res_out, void* __r
             v[i][2] = unpack_lo<kBf16>(q.y); v[i][3] = unpack_hi<kBf16>(q.y);
             v[i][4] = unpack_lo<kBf16>(q.z); v[i][5] = unpack_hi<kBf16>(q.z);
             v[i][6] = unpack_lo<kBf16>(q.w); v[i][7] = unpack_hi<kBf16>(q.w);
-            if (kDeltaF32 && peers.n > 0) {
-                const int64_t off = static_cast<int64_t>(r_in) * cols + vi * 8;
-                for (int s = 0; s < peers.n; ++s) {
-                    const float4* dp = reinterpret_cast<const float4*>(peers.src[s] + off);
-                    const float4 d0 = dp[0], d1 = dp[1];
-                    v[i][0] += d0.x; v[i][1] += d0.y; v[i][2] += d0.z; v[i][3] += d0.w;
-                    v[i][4] += d1.x; v[i][5] += d1.y; v[i][6] += d1.z; v[i][7] += d1.w;
-                }
-                if (peers.zero_buf != nullptr) {
-                    float4* zp = reinterpret_cast<float4*>(peers.zero_buf + off);
-                    zp[0] = make_float4(0.f, 0.f, 0.f, 0.f);
-                    zp[1] = make_float4(0.f, 0.f, 0.f, 0.f);
-                }
-#pragma unroll
-                for (int j = 0; j < 8; j += 2) {
-                    uint32_t p = pack2<kBf16>(v[i][j], v[i][j + 1]);
-                    v[i][j] = unpack_lo<kBf16>(p);
-                    v[i][j + 1] = unpack_hi<kBf16>(p);
-                }
-            } else if (delta != nullptr) {
+            if (delta != nullptr) {
                 if (kDeltaF32) {
                     float4* dp = reinterpret_cast<float4*>(reinterpret_cast<float*>(delta) +
                                                            static_cast<int64_t>(r_in) * cols + vi * 8);
@@ -183,12 +156,12 @@ norm_kernel(const void* __restrict__ x_in, void* delta, void* res_out, void* __r
 template <bool kBf16, bool kLayerNorm, bool kDeltaF32>
 static int launch_norm_vpt(int rows, int cols, const void* x, void* delta, void* res_out, void* out, const void* gamma,
                            const void* beta, const int32_t* row_idx, float eps, int zero_delta, int post_norm,
-                           int64_t ld_in, int64_t ld_out, const DeltaPeers& peers, cudaStream_t s) {
+                           int64_t ld_in, int64_t ld_out, cudaStream_t s) {
     const int nvec = cols / 8;
     const int vpt = (nvec + kNormThreads - 1) / kNormThreads;
 #define HDS_NORM_LAUNCH(V)                                                                                        \
     launch_kernel(norm_kernel<V, kBf16, kLayerNorm, kDeltaF32>, dim3(rows), dim3(kNormThreads), 0, s, x, delta,    \
-                  res_out, out, gamma, beta, row_idx, cols, eps, zero_delta, post_norm, ld_in, ld_out, peers)
+                  res_out, out, gamma, beta, row_idx, cols, eps, zero_delta, post_norm, ld_in, ld_out)
     if (vpt <= 1) HDS_NORM_LAUNCH(1);
     else if (vpt <= 2) HDS_NORM_LAUNCH(2);
     else if (vpt <= 4) HDS_NORM_LAUNCH(4);
@@ -198,6 +171,202 @@ static int launch_norm_vpt(int rows, int cols, const void* x, void* delta, void*
         return HDS_ERR_UNSUPPORTED;
     }
 #undef HDS_NORM_LAUNCH
+    HDS_CHECK_CUDA(cudaGetLastError());
+    return HDS_OK;
+}
+
+// ---------------------------------------------------------------------------------------------
+// Tensor-parallel norm: the collective that follows a row-parallel GEMM, fused with residual add + normalisation.
+//
+// Every rank's GEMM left its partial sums in its OWN buffer (symmetric memory) and released them with a flag
+// (tp_signal_tail). This kernel acquires all ranks' flags and then runs in one of two shapes:
+//   * all-reduce (scatter == 0, decode-size batches): every rank sums all ranks' partials for ALL rows — one pass of
+//     `multimem.ld_reduce` (the switch adds the ranks' copies) or plain 16-byte peer loads in rank order — adds them to
+//     its replica of the residual stream and normalises locally. One flag exchange per reduction, nothing else.
+//   * reduce-scatter + all-gather (scatter == 1, larger batches): a rank reduces only the rows it owns
+//     (n-times fewer NVLink bytes), keeps the residual stream of those rows, and writes the normalised rows into EVERY
+//     rank's activation buffer (`multimem.st`, or one store per peer); the last CTA then signals, and the consuming
+//     GEMM's TMA producer waits for all ranks' signals before its first activation load (all-gather -> GEMM).
+// fp32 partial sums (accumulating decode GEMMs) live in two alternating buffers; the kernel clears the one NOT being
+// read so the next accumulating GEMM starts from zero. 16-bit partials (store epilogues of the prefill GEMMs) need no
+// clearing. Replaces NCCL all-reduce + residual add + norm (llama_v2/model.py:159-170 in the reference).
+// ---------------------------------------------------------------------------------------------
+struct TpReduce {
+    const char* src[kTpMaxRanks];  // every rank's partial-sum buffer through this rank's mappings, rank order
+    const char* src_mc;            // NVLS alias of that buffer (multimem.ld_reduce), or null
+    char* out_peer[kTpMaxRanks];   // scatter: `out` on every rank (this rank's mappings)
+    char* out_mc;                  // scatter: NVLS alias of `out` (multimem.st), or null
+    float* zero_buf;               // local fp32 buffer to clear ([rows_total, cols]), may be null
+    int n;                         // ranks
+    int scatter;
+    int row0, n_rows;              // rows [row0, row0 + n_rows) are normalised by this launch
+    int rows_total;                // rows of the whole batch (extent of zero_buf)
+    TpSync sync;
+};
+
+template <int VPT, bool kBf16, bool kLayerNorm, bool kPartial16>
+__global__ void __launch_bounds__(kNormThreads)
+norm_tp_kernel(const void* __restrict__ x_in, void* res_out, void* __restrict__ out, const void* __restrict__ gamma,
+               const void* __restrict__ beta, int cols, float eps, int64_t ld_in, int64_t ld_out, const TpReduce tp) {
+    __shared__ float red[kNormThreads / 32];
+    pdl_enter();
+    if (tp.sync.wait) tp_wait_cta(tp.sync);
+    const int nvec = cols >> 3;
+    const bool live = static_cast<int>(blockIdx.x) < tp.n_rows;
+    const int r = tp.row0 + blockIdx.x;
+    if (tp.zero_buf != nullptr) {
+        // all-reduce shape: CTA r clears row r; scatter shape: the CTAs of this launch share all rows_total rows
+        const int step = tp.scatter ? static_cast<int>(gridDim.x) : tp.rows_total;
+        for (int rr = tp.scatter ? static_cast<int>(blockIdx.x) : r; rr < tp.rows_total; rr += step) {
+            float4* zp = reinterpret_cast<float4*>(tp.zero_buf + static_cast<int64_t>(rr) * cols);
+            for (int vi = threadIdx.x; vi < 2 * nvec; vi += kNormThreads) zp[vi] = make_float4(0.f, 0.f, 0.f, 0.f);
+        }
+    }
+    float v[VPT][8];
+    float sum = 0.0f, sumsq = 0.0f;
+    if (live) {
+        const char* xrow = reinterpret_cast<const char*>(x_in) + static_cast<int64_t>(r) * ld_in * 2;
+#pragma unroll
+        for (int i = 0; i < VPT; ++i) {
+            const int vi = threadIdx.x + i * kNormThreads;
+            if (vi < nvec) {
+                const uint4 q = *reinterpret_cast<const uint4*>(xrow + vi * 16);
+                v[i][0] = unpack_lo<kBf16>(q.x); v[i][1] = unpack_hi<kBf16>(q.x);
+                v[i][2] = unpack_lo<kBf16>(q.y); v[i][3] = unpack_hi<kBf16>(q.y);
+                v[i][4] = unpack_lo<kBf16>(q.z); v[i][5] = unpack_hi<kBf16>(q.z);
+                v[i][6] = unpack_lo<kBf16>(q.w); v[i][7] = unpack_hi<kBf16>(q.w);
+                const int64_t e = static_cast<int64_t>(r) * cols + vi * 8;  // element offset in a partial-sum buffer
+                if constexpr (kPartial16) {
+                    if (tp.src_mc != nullptr) {
+                        const uint4 d = multimem_ld_reduce_v4_h2<kBf16>(tp.src_mc + e * 2);
+                        v[i][0] += unpack_lo<kBf16>(d.x); v[i][1] += unpack_hi<kBf16>(d.x);
+                        v[i][2] += unpack_lo<kBf16>(d.y); v[i][3] += unpack_hi<kBf16>(d.y);
+                        v[i][4] += unpack_lo<kBf16>(d.z); v[i][5] += unpack_hi<kBf16>(d.z);
+                        v[i][6] += unpack_lo<kBf16>(d.w); v[i][7] += unpack_hi<kBf16>(d.w);
+                    } else {
+                        for (int s = 0; s < tp.n; ++s) {
+                            const uint4 d = ld_relaxed_sys_v4(tp.src[s] + e * 2);
+                            v[i][0] += unpack_lo<kBf16>(d.x); v[i][1] += unpack_hi<kBf16>(d.x);
+                            v[i][2] += unpack_lo<kBf16>(d.y); v[i][3] += unpack_hi<kBf16>(d.y);
+                            v[i][4] += unpack_lo<kBf16>(d.z); v[i][5] += unpack_hi<kBf16>(d.z);
+                            v[i][6] += unpack_lo<kBf16>(d.w); v[i][7] += unpack_hi<kBf16>(d.w);
+                        }
+                    }
+                } else {
+                    if (tp.src_mc != nullptr) {
+                        const float4 d0 = multimem_ld_reduce_v4_f32(tp.src_mc + e * 4);
+                        const float4 d1 = multimem_ld_reduce_v4_f32(tp.src_mc + e * 4 + 16);
+                        v[i][0] += d0.x; v[i][1] += d0.y; v[i][2] += d0.z; v[i][3] += d0.w;
+                        v[i][4] += d1.x; v[i][5] += d1.y; v[i][6] += d1.z; v[i][7] += d1.w;
+                    } else {
+                        for (int s = 0; s < tp.n; ++s) {
+                            const uint4 a = ld_relaxed_sys_v4(tp.src[s] + e * 4);
+                            const uint4 b = ld_relaxed_sys_v4(tp.src[s] + e * 4 + 16);
+                            v[i][0] += __uint_as_float(a.x); v[i][1] += __uint_as_float(a.y);
+                            v[i][2] += __uint_as_float(a.z); v[i][3] += __uint_as_float(a.w);
+                            v[i][4] += __uint_as_float(b.x); v[i][5] += __uint_as_float(b.y);
+                            v[i][6] += __uint_as_float(b.z); v[i][7] += __uint_as_float(b.w);
+                        }
+                    }
+                }
+                // the residual stream is stored in the 16-bit dtype: round before normalising
+#pragma unroll
+                for (int j = 0; j < 8; j += 2) {
+                    const uint32_t p = pack2<kBf16>(v[i][j], v[i][j + 1]);
+                    v[i][j] = unpack_lo<kBf16>(p);
+                    v[i][j + 1] = unpack_hi<kBf16>(p);
+                }
+#pragma unroll
+                for (int j = 0; j < 8; ++j) {
+                    sum += v[i][j];
+                    sumsq += v[i][j] * v[i][j];
+                }
+                if (res_out != nullptr) {
+                    uint4 o;
+                    o.x = pack2<kBf16>(v[i][0], v[i][1]); o.y = pack2<kBf16>(v[i][2], v[i][3]);
+                    o.z = pack2<kBf16>(v[i][4], v[i][5]); o.w = pack2<kBf16>(v[i][6], v[i][7]);
+                    *reinterpret_cast<uint4*>(reinterpret_cast<char*>(res_out) + (static_cast<int64_t>(r) * ld_out + vi * 8) * 2) = o;
+                }
+            }
+        }
+    }
+    float mean = 0.0f, rstd;
+    if (kLayerNorm) {
+        sum = block_sum_256(sum, red);
+        mean = sum / cols;
+        float var = 0.0f;
+        if (live) {
+#pragma unroll
+            for (int i = 0; i < VPT; ++i) {
+                const int vi = threadIdx.x + i * kNormThreads;
+                if (vi < nvec) {
+#pragma unroll
+                    for (int j = 0; j < 8; ++j) {
+                        const float d = v[i][j] - mean;
+                        var += d * d;
+                    }
+                }
+            }
+        }
+        var = block_sum_256(var, red);
+        rstd = rsqrtf(var / cols + eps);
+    } else {
+        sumsq = block_sum_256(sumsq, red);
+        rstd = rsqrtf(sumsq / cols + eps);
+    }
+    if (live) {
+#pragma unroll
+        for (int i = 0; i < VPT; ++i) {
+            const int vi = threadIdx.x + i * kNormThreads;
+            if (vi < nvec) {
+                const uint4 g = *reinterpret_cast<const uint4*>(reinterpret_cast<const char*>(gamma) + vi * 16);
+                const float gg[8] = {unpack_lo<kBf16>(g.x), unpack_hi<kBf16>(g.x), unpack_lo<kBf16>(g.y), unpack_hi<kBf16>(g.y),
+                                     unpack_lo<kBf16>(g.z), unpack_hi<kBf16>(g.z), unpack_lo<kBf16>(g.w), unpack_hi<kBf16>(g.w)};
+                float bb[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+                if (kLayerNorm && beta != nullptr) {
+                    const uint4 b = *reinterpret_cast<const uint4*>(reinterpret_cast<const char*>(beta) + vi * 16);
+                    bb[0] = unpack_lo<kBf16>(b.x); bb[1] = unpack_hi<kBf16>(b.x);
+                    bb[2] = unpack_lo<kBf16>(b.y); bb[3] = unpack_hi<kBf16>(b.y);
+                    bb[4] = unpack_lo<kBf16>(b.z); bb[5] = unpack_hi<kBf16>(b.z);
+                    bb[6] = unpack_lo<kBf16>(b.w); bb[7] = unpack_hi<kBf16>(b.w);
+                }
+                float o[8];
+#pragma unroll
+                for (int j = 0; j < 8; ++j) o[j] = (v[i][j] - mean) * rstd * gg[j] + bb[j];
+                uint4 q;
+                q.x = pack2<kBf16>(o[0], o[1]); q.y = pack2<kBf16>(o[2], o[3]);
+                q.z = pack2<kBf16>(o[4], o[5]); q.w = pack2<kBf16>(o[6], o[7]);
+                const int64_t off = (static_cast<int64_t>(r) * ld_out + vi * 8) * 2;
+                if (!tp.scatter) {
+                    *reinterpret_cast<uint4*>(reinterpret_cast<char*>(out) + off) = q;
+                } else if (tp.out_mc != nullptr) {
+                    multimem_st_v4(tp.out_mc + off, q);
+                } else {
+                    for (int s = 0; s < tp.n; ++s) st_v4(tp.out_peer[s] + off, q);
+                }
+            }
+        }
+    }
+    if (tp.sync.signal) tp_signal_tail(tp.sync, gridDim.x);
+}
+
+template <bool kBf16, bool kLayerNorm, bool kPartial16>
+static int launch_norm_tp_vpt(int grid, int cols, const void* x, void* res_out, void* out, const void* gamma, const void* beta,
+                              float eps, int64_t ld_in, int64_t ld_out, const TpReduce& tp, cudaStream_t s) {
+    const int nvec = cols / 8;
+    const int vpt = (nvec + kNormThreads - 1) / kNormThreads;
+#define HDS_NORM_TP_LAUNCH(V)                                                                                       \
+    launch_kernel(norm_tp_kernel<V, kBf16, kLayerNorm, kPartial16>, dim3(grid), dim3(kNormThreads), 0, s, x, res_out, \
+                  out, gamma, beta, cols, eps, ld_in, ld_out, tp)
+    if (vpt <= 1) HDS_NORM_TP_LAUNCH(1);
+    else if (vpt <= 2) HDS_NORM_TP_LAUNCH(2);
+    else if (vpt <= 4) HDS_NORM_TP_LAUNCH(4);
+    else if (vpt <= 8) HDS_NORM_TP_LAUNCH(8);
+    else {
+        set_error("norm_tp: cols > 16384 unsupported");
+        return HDS_ERR_UNSUPPORTED;
+    }
+#undef HDS_NORM_TP_LAUNCH
     HDS_CHECK_CUDA(cudaGetLastError());
     return HDS_OK;
 }
@@ -414,14 +583,15 @@ struct PeerPtrs {
     const char* p[8];
 };
 __global__ void p2p_gather_rows_kernel(char* __restrict__ dst, const PeerPtrs peers, int rows_per_peer, int n_rows,
-                                       int64_t row_bytes, int my_rank) {
+                                       int64_t row_bytes, int my_rank, const TpSync sync) {
+    if (sync.wait) tp_wait_cta(sync);  // every rank has published "my rows of this slot have landed"
     const int r = blockIdx.x;
     const int owner = r / rows_per_peer;
     if (r >= n_rows || owner == my_rank) return;
-    const uint4* src = reinterpret_cast<const uint4*>(peers.p[owner] + static_cast<int64_t>(r) * row_bytes);
+    const char* src = peers.p[owner] + static_cast<int64_t>(r) * row_bytes;
     uint4* d = reinterpret_cast<uint4*>(dst + static_cast<int64_t>(r) * row_bytes);
     const int nvec = static_cast<int>(row_bytes >> 4);
-    for (int i = threadIdx.x; i < nvec; i += blockDim.x) d[i] = src[i];
+    for (int i = threadIdx.x; i < nvec; i += blockDim.x) d[i] = ld_relaxed_sys_v4(src + i * 16);
 }
 
 // fp32 -> 16-bit convert (used to materialise accumulated fp32 partial sums), optional zeroing
@@ -448,35 +618,9 @@ __global__ void cvt_f32_kernel(float* __restrict__ src, void* __restrict__ dst, 
 
 using namespace hds;
 
-static int norm_impl(const void* x, int64_t ld_in, void* delta, int delta_is_f32, int zero_delta, void* res_out,
-                     void* out, int64_t ld_out, const void* gamma, const void* beta, const int32_t* row_idx, int rows,
-                     int cols, float eps, int layer_norm, int post_norm, int dtype, const DeltaPeers& peers, void* stream);
-
 extern "C" int hds_norm(const void* x, int64_t ld_in, void* delta, int delta_is_f32, int zero_delta, void* res_out,
                         void* out, int64_t ld_out, const void* gamma, const void* beta, const int32_t* row_idx,
                         int rows, int cols, float eps, int layer_norm, int post_norm, int dtype, void* stream) {
-    DeltaPeers none;
-    memset(&none, 0, sizeof(none));
-    return norm_impl(x, ld_in, delta, delta_is_f32, zero_delta, res_out, out, ld_out, gamma, beta, row_idx, rows, cols,
-                     eps, layer_norm, post_norm, dtype, none, stream);
-}
-
-extern "C" int hds_norm_tp(const void* x, int64_t ld_in, const float* const* delta_peer_ptrs, int n_peers,
-                           float* zero_buf, void* res_out, void* out, int64_t ld_out, const void* gamma,
-                           const void* beta, int rows, int cols, float eps, int layer_norm, int dtype, void* stream) {
-    HDS_REQUIRE(n_peers >= 1 && n_peers <= 8, "hds_norm_tp: 1..8 peer buffers");
-    DeltaPeers peers;
-    memset(&peers, 0, sizeof(peers));
-    for (int i = 0; i < n_peers; ++i) peers.src[i] = delta_peer_ptrs[i];
-    peers.n = n_peers;
-    peers.zero_buf = zero_buf;
-    return norm_impl(x, ld_in, const_cast<float*>(delta_peer_ptrs[0]), 1, 0, res_out, out, ld_out, gamma, beta, nullptr,
-                     rows, cols, eps, layer_norm, 0, dtype, peers, stream);
-}
-
-static int norm_impl(const void* x, int64_t ld_in, void* delta, int delta_is_f32, int zero_delta, void* res_out,
-                     void* out, int64_t ld_out, const void* gamma, const void* beta, const int32_t* row_idx, int rows,
-                     int cols, float eps, int layer_norm, int post_norm, int dtype, const DeltaPeers& peers, void* stream) {
     HDS_REQUIRE(rows >= 0 && cols > 0 && cols % 8 == 0, "hds_norm: cols must be a positive multiple of 8");
     HDS_REQUIRE(dtype == 0 || dtype == 1, "hds_norm: dtype must be 0 (bf16) or 1 (fp16)");
     HDS_REQUIRE(delta == nullptr || row_idx == nullptr, "hds_norm: delta and row gather are mutually exclusive");
@@ -485,7 +629,7 @@ static int norm_impl(const void* x, int64_t ld_in, void* delta, int delta_is_f32
     const bool f32 = delta != nullptr && delta_is_f32;
 #define HDS_NORM_DISPATCH(BF, LN, F32)                                                                            \
     return launch_norm_vpt<BF, LN, F32>(rows, cols, x, delta, res_out, out, gamma, beta, row_idx, eps, zero_delta, \
-                                        post_norm, ld_in, ld_out, peers, s)
+                                        post_norm, ld_in, ld_out, s)
     if (dtype == 0) {
         if (layer_norm) { if (f32) HDS_NORM_DISPATCH(true, true, true); else HDS_NORM_DISPATCH(true, true, false); }
         else            { if (f32) HDS_NORM_DISPATCH(true, false, true); else HDS_NORM_DISPATCH(true, false, false); }
@@ -494,6 +638,45 @@ static int norm_impl(const void* x, int64_t ld_in, void* delta, int delta_is_f32
         else            { if (f32) HDS_NORM_DISPATCH(false, false, true); else HDS_NORM_DISPATCH(false, false, false); }
     }
 #undef HDS_NORM_DISPATCH
+}
+
+extern "C" int hds_norm_tp(int ctx, int wait, int signal, const void* x, int64_t ld_in, const void* const* src_ptrs,
+                           const void* src_mc, int partial_16bit, float* zero_buf, void* res_out, void* out, int64_t ld_out,
+                           void* const* out_ptrs, void* out_mc, int row0, int n_rows, int rows_total, const void* gamma,
+                           const void* beta, int cols, float eps, int layer_norm, int dtype, void* stream) {
+    HDS_REQUIRE(cols > 0 && cols % 8 == 0, "hds_norm_tp: cols must be a positive multiple of 8");
+    HDS_REQUIRE(dtype == 0 || dtype == 1, "hds_norm_tp: dtype must be 0 (bf16) or 1 (fp16)");
+    HDS_REQUIRE(row0 >= 0 && n_rows >= 0 && row0 + n_rows <= rows_total, "hds_norm_tp: row range outside the batch");
+    TpReduce tp;
+    memset(&tp, 0, sizeof(tp));
+    if (!tp_get_context(ctx, &tp.sync)) return HDS_ERR_BAD_ARG;
+    tp.sync.wait = wait ? 1 : 0;
+    tp.sync.signal = signal ? 1 : 0;
+    tp.n = tp.sync.n_ranks;
+    for (int i = 0; i < tp.n; ++i) tp.src[i] = reinterpret_cast<const char*>(src_ptrs[i]);
+    tp.src_mc = reinterpret_cast<const char*>(src_mc);
+    tp.scatter = out_ptrs != nullptr || out_mc != nullptr;
+    if (out_ptrs != nullptr)
+        for (int i = 0; i < tp.n; ++i) tp.out_peer[i] = reinterpret_cast<char*>(out_ptrs[i]);
+    tp.out_mc = reinterpret_cast<char*>(out_mc);
+    tp.zero_buf = zero_buf;
+    tp.row0 = row0;
+    tp.n_rows = n_rows;
+    tp.rows_total = rows_total;
+    // a rank that owns no row of a tiny batch still takes part in the flag exchange (and clears its buffer)
+    const int grid = n_rows > 0 ? n_rows : 1;
+    if (n_rows == 0 && !wait && !signal && zero_buf == nullptr) return HDS_OK;
+    cudaStream_t s = static_cast<cudaStream_t>(stream);
+#define HDS_NORM_TP_DISPATCH(BF, LN, P16) \
+    return launch_norm_tp_vpt<BF, LN, P16>(grid, cols, x, res_out, out, gamma, beta, eps, ld_in, ld_out, tp, s)
+    if (dtype == 0) {
+        if (layer_norm) { if (partial_16bit) HDS_NORM_TP_DISPATCH(true, true, true); else HDS_NORM_TP_DISPATCH(true, true, false); }
+        else            { if (partial_16bit) HDS_NORM_TP_DISPATCH(true, false, true); else HDS_NORM_TP_DISPATCH(true, false, false); }
+    } else {
+        if (layer_norm) { if (partial_16bit) HDS_NORM_TP_DISPATCH(false, true, true); else HDS_NORM_TP_DISPATCH(false, true, false); }
+        else            { if (partial_16bit) HDS_NORM_TP_DISPATCH(false, false, true); else HDS_NORM_TP_DISPATCH(false, false, false); }
+    }
+#undef HDS_NORM_TP_DISPATCH
 }
 
 extern "C" int hds_rope_kv_append(const void* qkv, int64_t ld_qkv, void* q_out, void* kv_cache_layer,
@@ -575,8 +758,10 @@ extern "C" int hds_p2p_gather_rows(void* dst, const void* const* peer_ptrs, int 
     PeerPtrs pp;
     memset(&pp, 0, sizeof(pp));
     for (int i = 0; i < n_peers; ++i) pp.p[i] = reinterpret_cast<const char*>(peer_ptrs[i]);
+    TpSync sync = tp_take_armed();
+    sync.signal = 0;
     p2p_gather_rows_kernel<<<n_rows, 256, 0, static_cast<cudaStream_t>(stream)>>>(reinterpret_cast<char*>(dst), pp,
-                                                                                  rows_per_peer, n_rows, row_bytes, my_rank);
+                                                                                  rows_per_peer, n_rows, row_bytes, my_rank, sync);
     HDS_CHECK_CUDA(cudaGetLastError());
     return HDS_OK;
 }

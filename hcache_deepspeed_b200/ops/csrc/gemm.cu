@@ -3,6 +3,7 @@
 #include "gemm_core.cuh"
 #include "gemm_skinny.cuh"
 #include "hds_host.cuh"
+#include "tp_sync_host.cuh"
 #include "../../../include/hds_b200.h"
 
 namespace hds {
@@ -207,6 +208,7 @@ static int launch_skinny(int epi, bool bf16, const void* X, int64_t ldx, const v
     a.act = act;
     a.out = out; a.ldo = ldo; a.bias = bias;
     a.accum = accum; a.ld_accum = ld_accum;
+    a.sync = tp_take_armed();
     if (splits > 1 && epi != EPI_RED_F32) {
         a.ws = reinterpret_cast<float*>(ws);
         a.tickets = reinterpret_cast<int32_t*>(reinterpret_cast<char*>(ws) + ws_data);
@@ -328,6 +330,7 @@ extern "C" int hds_gemm(const void* A, int64_t lda, const void* W, int64_t ldw, 
     g.out = out;
     g.ldo = ldo;
     g.bias = bias;
+    g.sync = tp_take_armed();
     if (g.splits > 1) {
         g.splitk_ws = reinterpret_cast<float*>(splitk_ws);
         g.splitk_tickets = reinterpret_cast<int32_t*>(reinterpret_cast<char*>(splitk_ws) +
@@ -367,6 +370,7 @@ extern "C" int hds_gemm_accum(const void* A, int64_t lda, const void* W, int64_t
     g.n_targets = n_targets;
     g.red_mode = red_mode;
     g.ld_accum = ld_accum;
+    g.sync = tp_take_armed();
     const int grid = grid_for(g, bn);
     cudaStream_t s = static_cast<cudaStream_t>(stream);
     return dtype == 0 ? launch_gemm_bn<EPI_RED_F32, true>(bn, ops.ta, ops.tw, g, grid, s)
@@ -397,6 +401,7 @@ extern "C" int hds_moe_gemm(const void* A, int64_t lda, const void* W_stacked, i
     g.ldo = ldo;
     g.group_pad_off = pad_off;
     g.n_groups = n_experts;
+    g.sync = tp_take_armed();
     const int grid = grid_for(g, bn);
     cudaStream_t s = static_cast<cudaStream_t>(stream);
     if (dtype == 0) {
@@ -452,6 +457,7 @@ static int gemm_rope_common(bool has_q, const void* A, int64_t lda, const void* 
     g.n_kv_heads = n_kv_heads;
     g.block_size = block_size;
     g.do_rope = do_rope;
+    g.sync = tp_take_armed();
     if (pair)
         return gemm_2sm_dispatch_rope(g, A, lda * 2, W, ldw * 2, dtype == 0, has_q, static_cast<cudaStream_t>(stream));
     const int grid = grid_for(g, bn);

@@ -20,6 +20,7 @@
 #include <stdlib.h>
 #include "gemm_core.cuh"
 #include "hds_host.cuh"
+#include "tp_sync_host.cuh"
 #include "../../../include/hds_b200.h"
 
 namespace hds {
@@ -157,6 +158,10 @@ gemm_2sm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constan
 
     if (warp == 0) {
         if (lane == 0) {
+            if (args.sync.wait) {  // the activation operand was all-gathered into THIS GPU's buffer by the peers
+                tp_wait_thread(args.sync);
+                fence_proxy_async_global();
+            }
             uint32_t stage = 0, phase = 0;
             for (int w = pair; w < total_work; w += n_pairs) {
                 const int m_t = w % m_tiles, n_t = w / m_tiles;
@@ -263,6 +268,7 @@ gemm_2sm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constan
         tc_fence_after();
         tmem_dealloc_2sm<TMEM_COLS>(tmem_base);
     }
+    if (args.sync.signal) tp_signal_tail(args.sync, gridDim.x);
 }
 
 template <int BN, bool kFp8, bool kBf16, int EPI>
@@ -329,6 +335,7 @@ int gemm_2sm_dispatch(const void* A, int64_t lda_bytes, const float* a_scale, co
     fa.g.bias = bias;
     fa.a_scale = a_scale;
     fa.w_scale = w_scale;
+    fa.g.sync = tp_take_armed();
     CUtensorMap ta, tw;
     int rc;
     if (fp8) {

@@ -92,6 +92,10 @@ struct GemmArgs {
     // M is the row capacity of A / out; tiles at or beyond group_pad_off[n_groups] are skipped.
     const int32_t* group_pad_off;
     int n_groups;
+    // tensor-parallel flag protocol (hds_ptx.cuh): `sync.wait` — the TMA producer acquires every rank's latest signal
+    // before its first activation load (the operand was all-gathered into this GPU's buffer by the peers' norm kernels);
+    // `sync.signal` — the last CTA to retire releases this kernel's output to the peers.
+    TpSync sync;
 };
 
 // Expert that owns the 128-row tile starting at row0 (-1: past the last expert's rows).
@@ -436,6 +440,10 @@ gemm_tn_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
     if (warp == 0) {
         // ===================== TMA producer =====================
         if (lane == 0) {
+            if (args.sync.wait) {
+                tp_wait_thread(args.sync);
+                fence_proxy_async_global();
+            }
             uint32_t stage = 0, phase = 0;
             for (int w = blockIdx.x; w < total_work; w += gridDim.x) {
                 const int m_t = w % m_tiles;
@@ -561,6 +569,7 @@ gemm_tn_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
         tc_fence_after();
         tmem_dealloc<TMEM_COLS>(tmem_base);
     }
+    if (args.sync.signal) tp_signal_tail(args.sync, gridDim.x);
 }
 
 }  // namespace hds

@@ -13,6 +13,7 @@
 #include "gemm_core.cuh"
 #include "gemm_skinny.cuh"
 #include "hds_host.cuh"
+#include "tp_sync_host.cuh"
 #include "../../../include/hds_b200.h"
 
 namespace hds {
@@ -29,9 +30,10 @@ __host__ __device__ constexpr size_t f8_smem_bytes(int bn) {
 template <bool kBf16>
 __global__ void __launch_bounds__(256) quantize_fp8_rows_kernel(const void* __restrict__ x, int64_t ldx,
                                                                 uint8_t* __restrict__ q, int64_t ldq,
-                                                                float* __restrict__ scales, int K) {
+                                                                float* __restrict__ scales, int K, const TpSync sync) {
     __shared__ float red[8];
     pdl_enter();
+    if (sync.wait) tp_wait_cta(sync);  // tensor parallel: the rows were all-gathered into this buffer by the peers
     const int r = blockIdx.x;
     const char* row = reinterpret_cast<const char*>(x) + static_cast<int64_t>(r) * ldx * 2;
     uint8_t* qrow = q + static_cast<int64_t>(r) * ldq;
@@ -219,6 +221,7 @@ gemm_fp8_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constan
         tc_fence_after();
         tmem_dealloc<TMEM_COLS>(tmem_base);
     }
+    if (args.sync.signal) tp_signal_tail(args.sync, gridDim.x);
 }
 
 }  // namespace hds
@@ -264,12 +267,14 @@ extern "C" int hds_quantize_fp8_rows(const void* x, int64_t ldx, int rows, int K
     HDS_REQUIRE(rows >= 0 && K > 0, "hds_quantize_fp8_rows: bad shape");
     if (rows == 0) return HDS_OK;
     cudaStream_t s = static_cast<cudaStream_t>(stream);
+    TpSync sync = tp_take_armed();
+    sync.signal = 0;
     if (dtype == 0)
         HDS_CHECK_CUDA(launch_kernel(quantize_fp8_rows_kernel<true>, dim3(rows), dim3(K >= 8192 ? 256 : 128), 0, s, x, ldx,
-                                     reinterpret_cast<uint8_t*>(q), ldq, scales, K));
+                                     reinterpret_cast<uint8_t*>(q), ldq, scales, K, sync));
     else
         HDS_CHECK_CUDA(launch_kernel(quantize_fp8_rows_kernel<false>, dim3(rows), dim3(K >= 8192 ? 256 : 128), 0, s, x, ldx,
-                                     reinterpret_cast<uint8_t*>(q), ldq, scales, K));
+                                     reinterpret_cast<uint8_t*>(q), ldq, scales, K, sync));
     return HDS_OK;
 }
 
@@ -301,6 +306,7 @@ extern "C" int hds_gemm_fp8(const void* Aq, int64_t lda, const float* a_scale, c
     fa.g.bias = bias;
     fa.a_scale = a_scale;
     fa.w_scale = w_scale;
+    fa.g.sync = tp_take_armed();
     CUtensorMap ta, tw;
     int rc = make_tmap_2d_8b(&ta, Aq, K, M, lda, kF8BK, 128);
     if (rc) return rc;
@@ -403,6 +409,7 @@ extern "C" int hds_gemm_fp8_skinny(const void* Aq, int64_t lda, const float* a_s
     a.out = out; a.ldo = ldo; a.bias = bias;
     a.accum = accum; a.ld_accum = ld_accum;
     a.a_scale = a_scale; a.w_scale = w_scale;
+    a.sync = tp_take_armed();
     if (splits > 1 && epilogue != EPI_RED_F32) {
         a.ws = reinterpret_cast<float*>(ws);
         a.tickets = reinterpret_cast<int32_t*>(reinterpret_cast<char*>(ws) + ws_data);

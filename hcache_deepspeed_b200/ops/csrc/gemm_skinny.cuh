@@ -43,6 +43,7 @@ struct SkinnyArgs {
     int32_t* tickets;   // [n_tiles * 4], zero between calls
     const float* a_scale;  // fp8 operands only: per-token scales [M]
     const float* w_scale;  // fp8 operands only: per-feature scales [N]
+    TpSync sync;           // tensor parallel: the last CTA to retire releases the output to the peers (sync.signal)
 };
 
 template <int NT>
@@ -251,6 +252,7 @@ gemm_skinny_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_cons
         tc_fence_after();
         tmem_dealloc<TMEM_COLS>(tmem_base);
     }
+    if (args.sync.signal) tp_signal_tail(args.sync, gridDim.x);
 }
 
 }  // namespace hds

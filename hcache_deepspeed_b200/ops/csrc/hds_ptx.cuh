@@ -313,6 +313,122 @@ __device__ __forceinline__ void st_release_sys_u32(uint32_t* p, uint32_t v) {
     asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
 }
 
+__device__ __forceinline__ uint32_t ld_acquire_gpu_u32(const uint32_t* p) {
+    uint32_t v;
+    asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+    return v;
+}
+// 16-byte load that is never served from this SM's L1: the line may live in a peer GPU's memory (NVLink mapping) and
+// have been rewritten since an earlier kernel of this process touched it.
+__device__ __forceinline__ uint4 ld_relaxed_sys_v4(const void* p) {
+    uint4 r;
+    asm volatile("ld.relaxed.sys.global.v4.u32 {%0, %1, %2, %3}, [%4];"
+                 : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w)
+                 : "l"(p)
+                 : "memory");
+    return r;
+}
+// NVLS loads / stores on a multicast address: the switch sums the same offset of every GPU's buffer (ld_reduce) or
+// writes it to every GPU's buffer (st) — one instruction, one pass over this GPU's links.
+__device__ __forceinline__ float4 multimem_ld_reduce_v4_f32(const void* mc_ptr) {
+    float4 r;
+    asm volatile("multimem.ld_reduce.relaxed.sys.global.add.v4.f32 {%0, %1, %2, %3}, [%4];"
+                 : "=f"(r.x), "=f"(r.y), "=f"(r.z), "=f"(r.w)
+                 : "l"(mc_ptr)
+                 : "memory");
+    return r;
+}
+// 8 sixteen-bit values per instruction, summed in fp32 inside the switch, returned rounded to the 16-bit type
+template <bool kBf16>
+__device__ __forceinline__ uint4 multimem_ld_reduce_v4_h2(const void* mc_ptr) {
+    uint4 r;
+    if constexpr (kBf16)
+        asm volatile("multimem.ld_reduce.relaxed.sys.global.add.acc::f32.v4.bf16x2 {%0, %1, %2, %3}, [%4];"
+                     : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w)
+                     : "l"(mc_ptr)
+                     : "memory");
+    else
+        asm volatile("multimem.ld_reduce.relaxed.sys.global.add.acc::f32.v4.f16x2 {%0, %1, %2, %3}, [%4];"
+                     : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w)
+                     : "l"(mc_ptr)
+                     : "memory");
+    return r;
+}
+__device__ __forceinline__ void multimem_st_v4(void* mc_ptr, const uint4& v) {
+    asm volatile("multimem.st.relaxed.sys.global.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(mc_ptr), "r"(v.x), "r"(v.y),
+                 "r"(v.z), "r"(v.w)
+                 : "memory");
+}
+// generic-proxy writes to global memory (possibly made by another GPU) -> visible to this thread's later TMA loads
+__device__ __forceinline__ void fence_proxy_async_global() { asm volatile("fence.proxy.async.global;" ::: "memory"); }
+
+// --------------------------------------------------------------------------------------------
+// Tensor-parallel flag protocol (this library's own; no NCCL / torch kernel on the path).
+//
+// Every rank owns one 256-byte "pad" in symmetric memory:
+//     pad[r], r < 8 : arrive count of rank r — written ONLY by rank r (st.release.sys over NVLink), read only locally
+//     pad[kTpTicket]: CTA ticket of the kernel currently signalling (local use)
+//     pad[kTpSent]  : number of signals this rank has issued so far (local use)
+// All ranks run the same kernel sequence, so "signal" number n means the same program point on every rank. A SIGNAL
+// is issued by the last CTA of a kernel to retire (ticket), after a system-scope fence: everything the kernel wrote —
+// locally or into peers — is visible to whoever acquires the flag. A WAIT spins (locally, on this rank's own pad) until
+// every peer's arrive count has reached this rank's own `sent` count, i.e. until all ranks have passed the program
+// point of this rank's latest signal. Counters only grow (wrap-safe compare), nothing is ever reset, so there is no
+// second "everyone has left" phase, and a rank can run at most one signal ahead of the slowest one.
+// The waits are bounded: a protocol bug traps (CUDA error on the host) instead of hanging the GPU.
+// --------------------------------------------------------------------------------------------
+constexpr int kTpMaxRanks = 8;
+constexpr int kTpTicket = 32, kTpSent = 33;
+struct TpSync {
+    uint32_t* pad[kTpMaxRanks];  // pad[r]: rank r's pad through THIS rank's mapping; pad[rank] is local memory
+    int n_ranks, rank;
+    int wait;    // the kernel waits (before reading what peers produced) for every rank's latest signal
+    int signal;  // the kernel signals when its last CTA retires
+};
+
+__device__ __forceinline__ void tp_poll(const uint32_t* flag, uint32_t target) {
+    uint32_t probes = 0;
+    long long t0 = 0;
+    while (static_cast<int32_t>(ld_acquire_sys_u32(flag) - target) < 0) {
+        if ((++probes & 1023u) == 0) {
+            const long long now = clock64();
+            if (t0 == 0) t0 = now;
+            else if (now - t0 > (1ll << 35)) __trap();  // ~17 s: a peer died or the ranks ran different programs
+        }
+        if (probes > 64) __nanosleep(40);
+    }
+}
+// whole-CTA wait: one thread per peer spins, everybody leaves together
+__device__ __forceinline__ void tp_wait_cta(const TpSync& s) {
+    if (static_cast<int>(threadIdx.x) < s.n_ranks && static_cast<int>(threadIdx.x) != s.rank) {
+        const uint32_t target = ld_acquire_gpu_u32(s.pad[s.rank] + kTpSent);
+        tp_poll(s.pad[s.rank] + threadIdx.x, target);
+    }
+    __syncthreads();
+}
+// single-thread wait (TMA producer lanes); the caller orders the async proxy behind it
+__device__ __forceinline__ void tp_wait_thread(const TpSync& s) {
+    const uint32_t target = ld_acquire_gpu_u32(s.pad[s.rank] + kTpSent);
+    for (int r = 0; r < s.n_ranks; ++r)
+        if (r != s.rank) tp_poll(s.pad[s.rank] + r, target);
+}
+// Every thread of every CTA calls this once, after the CTA's last global write (it contains a __syncthreads).
+__device__ __forceinline__ void tp_signal_tail(const TpSync& s, uint32_t n_ctas) {
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        uint32_t* mine = s.pad[s.rank];
+        __threadfence_system();
+        if (atomicAdd(mine + kTpTicket, 1u) == n_ctas - 1) {
+            __threadfence_system();
+            const uint32_t v = ld_acquire_gpu_u32(mine + kTpSent) + 1;
+            *reinterpret_cast<volatile uint32_t*>(mine + kTpTicket) = 0;
+            *reinterpret_cast<volatile uint32_t*>(mine + kTpSent) = v;
+            for (int r = 0; r < s.n_ranks; ++r)
+                if (r != s.rank) st_release_sys_u32(s.pad[r] + s.rank, v);
+        }
+    }
+}
+
 // --------------------------------------------------------------------------------------------
 // numeric helpers
 // --------------------------------------------------------------------------------------------

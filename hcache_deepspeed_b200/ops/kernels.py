@@ -136,8 +136,9 @@ def gemm(a: torch.Tensor, w: torch.Tensor, bias: Optional[torch.Tensor] = None, 
 def gemm_accum(a: torch.Tensor, w: torch.Tensor, accum: torch.Tensor, bias: Optional[torch.Tensor] = None,
                peer_ptrs: Optional[Sequence[int]] = None, multicast_ptr: Optional[int] = None, bn: int = 0,
                splits: int = 0) -> None:
-    """``accum (fp32) += a @ w.T``; with ``peer_ptrs`` / ``multicast_ptr`` the epilogue reduces into every
-    tensor-parallel rank's buffer over NVLink (fused GEMM -> all-reduce)."""
+    """``accum (fp32) += a @ w.T``. With ``peer_ptrs`` / ``multicast_ptr`` the epilogue adds its tile into every
+    tensor-parallel rank's buffer (``red.sys`` / ``multimem.red``: the push form of GEMM -> all-reduce; the serving path
+    uses the pull form — local accumulation, flag signal, reduction in :func:`norm_tp`)."""
     _check_2d(a, "a")
     M, K = a.shape
     N = w.shape[0]
@@ -221,17 +222,73 @@ def norm(x: torch.Tensor, gamma: torch.Tensor, out: torch.Tensor, *, beta: Optio
     return out
 
 
-def norm_tp(x: torch.Tensor, gamma: torch.Tensor, out: torch.Tensor, delta_peer_ptrs: Sequence[int], *,
-            zero_buf: Optional[torch.Tensor] = None, beta: Optional[torch.Tensor] = None,
-            res_out: Optional[torch.Tensor] = None, eps: float = 1e-5, layer_norm: bool = False) -> torch.Tensor:
-    """Norm whose pending delta is the sum of every TP rank's fp32 partial-sum buffer, read over NVLink."""
+def _ptr_array(ptrs: Optional[Sequence[int]]):
+    if ptrs is None:
+        return None
+    return (ctypes.c_void_p * len(ptrs))(*[int(p) for p in ptrs])
+
+
+def norm_tp(ctx: int, x: torch.Tensor, gamma: torch.Tensor, out: torch.Tensor, src_ptrs: Sequence[int], *,
+            src_mc: Optional[int] = None, partial_16bit: bool = False, zero_buf: Optional[torch.Tensor] = None,
+            beta: Optional[torch.Tensor] = None, res_out: Optional[torch.Tensor] = None, out_ptrs: Optional[Sequence[int]] = None,
+            out_mc: Optional[int] = None, row0: int = 0, n_rows: Optional[int] = None, wait: bool = True, signal: bool = False,
+            eps: float = 1e-5, layer_norm: bool = False) -> torch.Tensor:
+    """The collective after a row-parallel GEMM fused with residual add + norm (``hds_norm_tp``): all-reduce shape
+    (``out_ptrs`` / ``out_mc`` unset: every rank reduces all rows) or reduce-scatter + all-gather shape (this rank reduces
+    rows ``[row0, row0 + n_rows)`` and writes their normalised values into every rank's ``out``)."""
     cols = x.shape[-1]
-    arr = (ctypes.c_void_p * len(delta_peer_ptrs))(*delta_peer_ptrs)
+    total = x.numel() // cols
+    n = total if n_rows is None else n_rows
     lib = native.cuda_lib()
-    rc = lib.hds_norm_tp(_p(x), x.stride(-2) if x.dim() > 1 else cols, arr, len(delta_peer_ptrs), _p(zero_buf), _p(res_out),
-                         _p(out), out.stride(-2) if out.dim() > 1 else cols, _p(gamma), _p(beta), x.numel() // cols, cols,
-                         eps, 1 if layer_norm else 0, _dt(x), _stream())
+    rc = lib.hds_norm_tp(ctx, int(wait), int(signal), _p(x), x.stride(-2) if x.dim() > 1 else cols, _ptr_array(src_ptrs),
+                         src_mc, int(partial_16bit), _p(zero_buf), _p(res_out), _p(out), out.stride(-2) if out.dim() > 1 else cols,
+                         _ptr_array(out_ptrs), out_mc, row0, n, total, _p(gamma), _p(beta), cols, eps, 1 if layer_norm else 0,
+                         _dt(x), _stream())
     native.check(rc, "hds_norm_tp")
+    _count()
+    return out
+
+
+# ---- tensor-parallel flag protocol (tp_comm.cu) ------------------------------------------------------------------------
+def tp_ctx_create(rank: int, n_ranks: int, pad_ptrs: Sequence[int]) -> int:
+    ctx = native.cuda_lib().hds_tp_ctx_create(rank, n_ranks, _ptr_array(pad_ptrs))
+    if ctx < 0:
+        native.check(ctx, "hds_tp_ctx_create")
+    return ctx
+
+
+def tp_ctx_destroy(ctx: int) -> None:
+    native.cuda_lib().hds_tp_ctx_destroy(ctx)
+
+
+def tp_arm(ctx: int, wait: bool, signal: bool) -> None:
+    """Attach a flag wait / signal to the NEXT GEMM-family kernel this thread launches (see ``hds_tp_arm``)."""
+    native.check(native.cuda_lib().hds_tp_arm(ctx, int(wait), int(signal)), "hds_tp_arm")
+
+
+def tp_disarm() -> bool:
+    return bool(native.cuda_lib().hds_tp_disarm())
+
+
+def tp_signal(ctx: int) -> None:
+    native.check(native.cuda_lib().hds_tp_signal(ctx, _stream()), "hds_tp_signal")
+    _count()
+
+
+def tp_wait(ctx: int) -> None:
+    native.check(native.cuda_lib().hds_tp_wait(ctx, _stream()), "hds_tp_wait")
+    _count()
+
+
+def tp_gather_cols(ctx: int, out: torch.Tensor, src_ptrs: Sequence[int], ld_src: int, col0: Sequence[int],
+                   width: Sequence[int], rows: int, wait: bool = True) -> torch.Tensor:
+    """``out[:rows, col0[p]:col0[p]+width[p]] = rank p's slice`` for every rank (vocabulary-sharded logits all-gather)."""
+    n = len(src_ptrs)
+    c0 = (ctypes.c_int32 * n)(*col0)
+    wd = (ctypes.c_int32 * n)(*width)
+    rc = native.cuda_lib().hds_tp_gather_cols(ctx, int(wait), _p(out), out.stride(0), _ptr_array(src_ptrs), ld_src, c0, wd, rows,
+                                              out.element_size(), _stream())
+    native.check(rc, "hds_tp_gather_cols")
     _count()
     return out
 

@@ -41,7 +41,15 @@ def _declare_cuda(lib: ctypes.CDLL) -> None:
         "hds_qkv_rope_proj": [P, L, P, L, I, I, I, P, P, P, P, P, P, I, I, I, I, I, P],
         "hds_restore_kv_proj_peers": [P, I, I, L, P, L, I, I, I, P, P, P, P, P, I, I, I, I, P],
         "hds_norm": [P, L, P, I, I, P, P, L, P, P, P, I, I, F, I, I, I, P],
-        "hds_norm_tp": [P, L, P, I, P, P, P, L, P, P, I, I, F, I, I, P],
+        "hds_norm_tp": [I, I, I, P, L, P, P, I, P, P, P, L, P, P, I, I, I, P, P, I, F, I, I, P],
+        "hds_tp_ctx_create": [I, I, P],
+        "hds_tp_ctx_destroy": [I],
+        "hds_tp_arm": [I, I, I],
+        "hds_tp_disarm": [],
+        "hds_tp_signal": [I, P],
+        "hds_tp_wait": [I, P],
+        "hds_tp_barrier": [I, P],
+        "hds_tp_gather_cols": [I, I, P, L, P, L, P, P, I, I, P],
         "hds_rope_kv_append": [P, L, P, P, P, P, P, I, I, I, I, I, I, I, I, P],
         "hds_embed": [P, P, P, P, I, I, P, I, I, I, I, P],
         "hds_gather_rows": [P, P, P, I, I, P],
@@ -80,7 +88,6 @@ def _declare_cuda(lib: ctypes.CDLL) -> None:
     lib.hds_moe_padded_rows.restype = c_int64
     # optional entry points (declared when present so older builds keep loading)
     optional = {
-        "hds_tp_barrier": ([P, I, I, P], c_int),
         "hds_memset_u32": ([P, c_int32, L, P], c_int),
     }
     for name, (argtypes, restype) in optional.items():

@@ -89,15 +89,56 @@ int hds_norm(const void* x, int64_t ld_in, void* delta, int delta_is_f32, int ze
              int64_t ld_out, const void* gamma, const void* beta, const int32_t* row_idx, int rows, int cols,
              float eps, int layer_norm, int post_norm, int dtype, void* stream);
 
-/* Tensor-parallel variant: the pending delta is the SUM over ranks of an fp32 buffer that each rank accumulated
- * locally (hds_gemm_accum, red_mode 0) in symmetric memory. delta_peer_ptrs (HOST array) holds this rank's mappings
- * of that buffer on all n_peers ranks; the kernel adds them up with loads over NVLink (pull all-reduce fused into the
- * norm). zero_buf (optional) is a local rows x cols fp32 buffer to clear — the other half of the alternating pair.
- * The caller places a device barrier between the GEMMs and this kernel.
- * Ref: the dist.all_reduce + pre-norm pair of model_implementations/llama_v2/model.py:159-171. */
-int hds_norm_tp(const void* x, int64_t ld_in, const float* const* delta_peer_ptrs, int n_peers, float* zero_buf,
-                void* res_out, void* out, int64_t ld_out, const void* gamma, const void* beta, int rows, int cols,
-                float eps, int layer_norm, int dtype, void* stream);
+/* ---- tensor parallelism: this library's own flag protocol over symmetric memory ------------------------------------
+ *
+ * Every rank owns a 256-byte, zero-initialised "pad" in memory that all ranks of the group have mapped (symmetric
+ * memory / CUDA IPC / cuMemMap): 8 arrive counters written only by the respective peer, plus a ticket and a signal
+ * count used locally. A SIGNAL ("everything my kernels wrote so far is visible to you") is issued by the last CTA of
+ * a kernel to retire; a WAIT spins on the local pad until every peer has issued as many signals as this rank has.
+ * All ranks must run the same sequence of signalling kernels. Waits are bounded (~17 s) and trap on timeout.
+ * No reference counterpart: the reference calls NCCL (model_implementations/llama_v2/model.py:159-160, 168-169, 195-197).
+ *
+ * hds_tp_ctx_create: pad_ptrs is a HOST array [n_ranks] of this rank's mappings of every rank's pad
+ * (pad_ptrs[rank] = the local one). Returns a context id >= 0, or a negative error.
+ * hds_tp_arm: attaches a wait and / or a signal to the NEXT kernel this host thread launches through hds_gemm,
+ * hds_gemm_accum, hds_gemm_2sm, hds_gemm_fp8, hds_gemm_fp8_skinny, hds_moe_gemm, hds_qkv_rope_proj,
+ * hds_restore_kv_proj, hds_quantize_fp8_rows (wait only) or hds_p2p_gather_rows (wait only):
+ *   wait   - the kernel's TMA producer (or every CTA) acquires all ranks' flags before it reads activations that
+ *            the peers wrote into this GPU's buffer (all-gather -> GEMM);
+ *   signal - the kernel's last CTA releases its output to the peers (GEMM -> all-reduce / reduce-scatter).
+ * hds_tp_disarm returns 1 if an armed state was still pending (i.e. the intended launch did not consume it).
+ * hds_tp_signal / hds_tp_wait: one-CTA kernels; hds_tp_barrier = signal followed by wait. */
+int hds_tp_ctx_create(int rank, int n_ranks, void* const* pad_ptrs);
+int hds_tp_ctx_destroy(int ctx);
+int hds_tp_arm(int ctx, int wait, int signal);
+int hds_tp_disarm(void);
+int hds_tp_signal(int ctx, void* stream);
+int hds_tp_wait(int ctx, void* stream);
+int hds_tp_barrier(int ctx, void* stream);
+
+/* The collective after a row-parallel GEMM, fused with residual add + norm. src_ptrs (HOST array [n_ranks]): this
+ * rank's mappings of every rank's partial-sum buffer [rows_total, cols] (fp32, or the 16-bit I/O dtype when
+ * partial_16bit); src_mc: NVLS multicast alias of that buffer or NULL (then peers are read one by one, rank order).
+ *   out_ptrs == NULL and out_mc == NULL : all-reduce shape. Rows [row0, row0+n_rows) (normally all of them) are reduced
+ *       over all ranks, added to x (the local residual replica), written to res_out and normalised into the local `out`.
+ *   otherwise                           : reduce-scatter + all-gather shape. This rank reduces only rows
+ *       [row0, row0+n_rows) — the rows it owns —, keeps their residual in res_out, and writes the normalised rows into
+ *       every rank's `out` (out_mc: multicast alias -> multimem.st; else out_ptrs[r] one by one). Use signal = 1 and arm
+ *       the consuming GEMM with wait = 1.
+ * zero_buf (optional, local fp32 [rows_total, cols]): cleared — the idle half of the alternating accumulation pair.
+ * wait = 1: acquire every rank's flag first (the producing GEMMs were armed with signal = 1).
+ * Ref: dist.all_reduce + residual + norm of model_implementations/llama_v2/model.py:159-171. */
+int hds_norm_tp(int ctx, int wait, int signal, const void* x, int64_t ld_in, const void* const* src_ptrs,
+                const void* src_mc, int partial_16bit, float* zero_buf, void* res_out, void* out, int64_t ld_out,
+                void* const* out_ptrs, void* out_mc, int row0, int n_rows, int rows_total, const void* gamma,
+                const void* beta, int cols, float eps, int layer_norm, int dtype, void* stream);
+
+/* All-gather of column-sharded rows (vocabulary-sharded logits): out[row, col0[p] : col0[p]+width[p]] = rank p's
+ * slice buffer [rows, ld_src] for every p, pulled with 16-byte loads over NVLink. src_ptrs: HOST array of this rank's
+ * mappings; col0 / width: HOST arrays [n_ranks] in elements. wait = 1: acquire the flags the LM-head GEMMs signalled.
+ * Ref: dist.all_gather_into_tensor + permute copy, model_implementations/llama_v2/model.py:195-197. */
+int hds_tp_gather_cols(int ctx, int wait, void* out, int64_t ld_out, const void* const* src_ptrs, int64_t ld_src,
+                       const int32_t* col0, const int32_t* width, int rows, int elem_bytes, void* stream);
 
 /* ---- ragged helpers ------------------------------------------------------------------------ */
 
@@ -126,6 +167,7 @@ int hds_kv_blocks_copy(void* cache, void* staging, const int32_t* block_ids, int
 
 /* Row gather across tensor-parallel peers: rows [p*rows_per_peer, (p+1)*rows_per_peer) of `dst` are copied from the
  * same rows of peer p's buffer (peer_ptrs[p]: HOST array of this rank's mappings), except this rank's own rows.
+ * hds_tp_arm(ctx, 1, 0) before the call makes the kernel wait for every rank's "rows landed" signal first.
  * No reference counterpart (the reference has no TP restore). */
 int hds_p2p_gather_rows(void* dst, const void* const* peer_ptrs, int n_peers, int rows_per_peer, int n_rows,
                         int64_t row_bytes, int my_rank, void* stream);
