@@ -52,7 +52,7 @@ def run_reference_arm(a) -> None:
     dev = torch.device("cuda", local)
     os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
     os.environ.setdefault("MASTER_PORT", "29511")
-    tp = world if getattr(a, "parallelism", "dp") == "tp" else 1   # same layout as the other arm: dp = one replica per GPU
+    tp = world if getattr(a, "parallelism", "tp") == "tp" else 1   # same layout as the other arm (tp: stock AutoTP + NCCL)
     replicas = world // tp
     B, ctx, n_new, D = a.sessions * tp, a.ctx, a.new_tokens, a.decode_steps
     try:
@@ -74,6 +74,7 @@ def run_reference_arm(a) -> None:
     g = torch.Generator().manual_seed(7)
     prompt = torch.randint(0, 32000, (ctx + n_new, ), generator=g).pin_memory()  # restored ctx + new turn, recomputed
     ev = lambda: torch.cuda.Event(enable_timing=True)  # noqa: E731
+    host_stage = torch.empty((B, 1), dtype=torch.long).pin_memory()
 
     @torch.no_grad()
     def one_step(rec):
@@ -91,14 +92,16 @@ def run_reference_arm(a) -> None:
             del out
         # batched KV cache for the decode phase (one batched prefill; part of the step, not of TTFT/decode)
         ids = prompt.to(dev, non_blocking=True)[None].repeat(B, 1)
-        out = engine(input_ids=ids, use_cache=True)
+        out = engine(input_ids=ids, use_cache=True, logits_to_keep=1)   # last-position logits only (B x ctx x vocab would be 17 GB at B=64)
         cache = out.past_key_values
         cur = out.logits[:, -1].argmax(-1, keepdim=True)
+        torch.cuda.synchronize()                       # the batched prefill above is not part of the decode clock
         d0, d1, th = ev(), ev(), time.perf_counter()
         d0.record()
         for _ in range(D):
-            host_ids = cur.cpu().pin_memory()          # D2H of the sampled ids, H2D of the next inputs
-            out = engine(input_ids=host_ids.to(dev, non_blocking=True), past_key_values=cache, use_cache=True)
+            host_stage.copy_(cur, non_blocking=True)   # D2H of the sampled ids into the pinned staging buffer ...
+            torch.cuda.current_stream().synchronize()
+            out = engine(input_ids=host_stage.to(dev, non_blocking=True), past_key_values=cache, use_cache=True)  # ... and H2D
             cache = out.past_key_values
             cur = out.logits[:, -1].argmax(-1, keepdim=True)
         cur.cpu()
@@ -139,8 +142,9 @@ def run_reference_arm(a) -> None:
             "ms_per_step": round(total_ms / a.steps, 3), "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
             "dtype": "bf16", "data": "synthetic tokens, random-init weights", "impl": "reference",
             "ttft_p50_ms": round(ttft_dev, 3),
-            "reference_path": "deepspeed.init_inference (v1, no kernel injection) over HF LlamaForCausalLM; context re-established "
-                              "by recompute because the v2/HCache engine cannot run on sm_100 (see BASELINE.md §3)",
+            "reference_path": "deepspeed.init_inference (v1, no kernel injection" + (f", AutoTP + NCCL all-reduce at tp={tp}" if tp > 1 else "") +
+                              ") over HF LlamaForCausalLM; ttft_p50_ms is RECOMPUTE time-to-first-token: the context is re-established "
+                              "by recomputing the prompt because the v2/HCache engine cannot run on sm_100 (see BASELINE.md §3)",
             "config": {"model": a.model, "global_batch": B * replicas, "seq_len": ctx + n_new + D,
                        "parallelism": f"tp{tp}" if replicas == 1 else f"dp{replicas}",
                        "restored_ctx": ctx, "new_turn_tokens": n_new, "decode_steps": D, "sessions_per_gpu": a.sessions},

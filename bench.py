@@ -38,10 +38,10 @@ def parse():
     p.add_argument("--new-tokens", type=int, default=64, help="tokens of the new turn's prompt")
     p.add_argument("--decode-steps", type=int, default=32)
     p.add_argument("--sessions", type=int, default=8, help="concurrent sessions PER GPU (weak scaling: global batch = sessions x gpus)")
-    p.add_argument("--parallelism", default="dp", choices=["dp", "tp"],
-                   help="N > 1: 'dp' = one full replica per GPU serving its own sessions (a 7B model fits 13x in 180 GB; "
-                        "what a deployment does for throughput), 'tp' = one engine tensor-parallel over all GPUs (fused "
-                        "NVLink collectives, PCIe-sharded restore: lower TTFT, lower aggregate throughput)")
+    p.add_argument("--parallelism", default="tp", choices=["tp", "dp"],
+                   help="N > 1: 'tp' (default, the headline metric: decode tokens/s at TP = N) = one engine tensor-parallel over "
+                        "all GPUs (flag-protocol NVLink collectives, PCIe-sharded restore); 'dp' = one full replica per GPU "
+                        "serving its own sessions (no collective on the path; secondary)")
     p.add_argument("--source", default="dram", choices=["dram", "nvme"],
                    help="where a session's hidden states live before the restore: pinned host DRAM (headline) or a file read "
                         "back through the O_DIRECT aio engine inside the timed region (NVMe tier)")
@@ -125,9 +125,13 @@ def run_ours(a):
                                          "size": int((B + 1) * (max_ctx + 128) * spec.kv_bytes_per_token_layer() * spec.n_layers / tp)}},
         hcache={"enabled": True, "capture": "off", "shard_capture": tp > 1},
         quantization={"quantization_mode": None if a.quant == "none" else a.quant})
+    if tp > 1:
+        os.environ.setdefault("HDS_TP_STRICT", "1")   # the headline run must not silently fall back to NCCL collectives
     eng = build_engine_from_arch(spec, cfg, seed=1234, dtype=torch.bfloat16, device=dev)
     model = eng.model()
     assert native.cuda_lib_loaded(), "sm_100a kernel library was not loaded"
+    if tp > 1 and os.environ.get("HDS_TP_STRICT") == "1":
+        assert getattr(model.comm, "fused", False), "tensor-parallel run without the fused flag-protocol collectives"
 
     # synthetic host-DRAM hidden-state cache: one pinned [L, ctx, H] tensor (every session H2Ds its own copy)
     g = torch.Generator().manual_seed(7)
@@ -285,15 +289,17 @@ def run_ours(a):
             "ttft_p50_ms": round(ttft_dev, 3),
             "config": {"model": a.model, "global_batch": B * replicas, "seq_len": ctx + n_new + D,
                        "parallelism": f"tp{tp}" if replicas == 1 else f"dp{replicas}",
-                       "restored_ctx": ctx, "new_turn_tokens": n_new, "decode_steps": D, "sessions_per_gpu": a.sessions,
-                       "numa_bound_cpus": len(numa_cpus), "hidden_state_source": a.source if nvme is not None or a.source == "dram" else "dram",
-                       "restore_plan": {"recompute_prefix_layers": 0 if sharded else len(recompute_layers),
-                                        "hidden_state_layers": spec.n_layers if sharded else len(hidden_layers),
-                                        "kv_offload_layers": 0 if sharded else len(kv_layers), "tp_sharded_restore": sharded,
-                                        "host_link_GBps": round(link.io_bytes_per_s / 1e9, 1),
-                                        "tp_collectives": "fused GEMM-epilogue reduction" if bool(getattr(model.comm, "fused", False))
-                                        else ("nccl" if tp > 1 else "none")},
-                       "l2_policy": f"working set per step (weights {model.w.n_bytes() / 2**30:.1f} GiB + KV) exceeds the 126 MB L2"},
+                       "restored_ctx": ctx, "new_turn_tokens": n_new, "decode_steps": D, "sessions_per_gpu": a.sessions},
+            "details": {"numa_bound_cpus": len(numa_cpus), "hidden_state_source": a.source if nvme is not None or a.source == "dram" else "dram",
+                        "restore_plan": {"recompute_prefix_layers": 0 if sharded else len(recompute_layers),
+                                         "hidden_state_layers": spec.n_layers if sharded else len(hidden_layers),
+                                         "kv_offload_layers": 0 if sharded else len(kv_layers), "tp_sharded_restore": sharded,
+                                         "host_link_GBps": round(link.io_bytes_per_s / 1e9, 1)},
+                        "tp_collectives": ("flag protocol: GEMM tail signal + " + ("multimem.ld_reduce/st" if getattr(model.comm, "use_nvls", False)
+                                                                                 else "peer loads/stores") + " inside the norm kernel")
+                        if bool(getattr(model.comm, "fused", False)) else ("nccl" if tp > 1 else "none"),
+                        "decode_ms_per_iteration": round(dec_dev_ms / (a.steps * D), 4),
+                        "l2_policy": f"working set per step (weights {model.w.n_bytes() / 2**30:.1f} GiB + KV) exceeds the 126 MB L2"},
             "e2e": {"value": round(dec_tokens / (dec_host_ms / 1e3), 2), "unit": "tokens/s", "ttft_p50_ms": round(ttft_host, 3),
                     "h2d_bytes_per_step": h2d_step * replicas, "d2h_bytes_per_step": d2h_step * replicas},
             "gpu_launches": int(launches.item()),

@@ -18,7 +18,8 @@ struct TpContext {
     bool used;
     TpSync base;  // pads + rank geometry; wait / signal cleared
 };
-static TpContext g_tp_ctx[16];
+constexpr int kTpMaxContexts = 64;
+static TpContext g_tp_ctx[kTpMaxContexts];
 static std::mutex g_tp_mu;
 static thread_local TpSync g_tp_armed;
 static thread_local bool g_tp_armed_valid = false;
@@ -34,7 +35,7 @@ TpSync tp_take_armed() {
 }
 
 bool tp_get_context(int ctx, TpSync* out) {
-    if (ctx < 0 || ctx >= 16 || !g_tp_ctx[ctx].used) {
+    if (ctx < 0 || ctx >= kTpMaxContexts || !g_tp_ctx[ctx].used) {
         set_error("tensor-parallel context id is not valid");
         return false;
     }
@@ -89,7 +90,7 @@ using namespace hds;
 extern "C" int hds_tp_ctx_create(int rank, int n_ranks, void* const* pad_ptrs) {
     HDS_REQUIRE(n_ranks >= 1 && n_ranks <= kTpMaxRanks && rank >= 0 && rank < n_ranks, "hds_tp_ctx_create: 1..8 ranks");
     std::lock_guard<std::mutex> lock(g_tp_mu);
-    for (int i = 0; i < 16; ++i) {
+    for (int i = 0; i < kTpMaxContexts; ++i) {
         if (g_tp_ctx[i].used) continue;
         TpSync& b = g_tp_ctx[i].base;
         memset(&b, 0, sizeof(b));
@@ -103,13 +104,13 @@ extern "C" int hds_tp_ctx_create(int rank, int n_ranks, void* const* pad_ptrs) {
         g_tp_ctx[i].used = true;
         return i;
     }
-    set_error("hds_tp_ctx_create: all 16 context slots are taken");
+    set_error("hds_tp_ctx_create: all 64 context slots are taken (hds_tp_ctx_destroy releases one)");
     return HDS_ERR_TOO_LARGE;
 }
 
 extern "C" int hds_tp_ctx_destroy(int ctx) {
     std::lock_guard<std::mutex> lock(g_tp_mu);
-    if (ctx >= 0 && ctx < 16) g_tp_ctx[ctx].used = false;
+    if (ctx >= 0 && ctx < kTpMaxContexts) g_tp_ctx[ctx].used = false;
     return HDS_OK;
 }
 

@@ -97,6 +97,19 @@ class FlagTPComm(TPComm):
         self.pad = self.alloc_symmetric((PAD_WORDS, ), torch.int32)
         self.ctx = kernels.tp_ctx_create(self.rank, self.size, self.peer_ptrs_raw(self.pad))
 
+    def close(self) -> None:
+        """Release the library-side context slot (the buffers go with the tensors)."""
+        if self.ctx >= 0:
+            from ..ops import kernels
+            kernels.tp_ctx_destroy(self.ctx)
+            self.ctx = -1
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
     def arm(self, wait: bool = False, signal: bool = False) -> None:
         """Attach a flag wait / signal to the next GEMM-family launch of this thread."""
         from ..ops import kernels

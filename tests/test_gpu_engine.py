@@ -220,3 +220,33 @@ def test_layer_pipelined_kv_reload(kinds):
                         kv_layer_major=True, recompute_layers=rl, defer=True)
     eng.flush(12)                                    # never followed by a forward: flush completes the transfers
     torch.cuda.synchronize()
+
+
+def test_decode_graph_capture_survives_garbage_collection():
+    """Regression: Python's cyclic collector finalising an old CUDAGraph inside an open capture invalidated the capture
+    (cudaErrorStreamCaptureInvalidated, order-dependent). The capture helper collects first and keeps the collector off."""
+    import gc
+    from hcache_deepspeed_b200.inference.v2 import build_engine_from_arch
+    from hcache_deepspeed_b200.models.arch import named_arch
+    from hcache_deepspeed_b200.utils.cuda_graph import capture
+
+    class Holder:
+        pass
+
+    x = torch.ones(64, device="cuda")
+    for _ in range(4):           # dead reference cycles that own live CUDA graphs
+        h = Holder()
+        h.me = h
+        h.graph, _ = capture(lambda: x * 2)
+    del h
+    spec = named_arch("llama-2-7b").scaled(n_layers=2)
+    eng = build_engine_from_arch(spec, _cfg(T=256, ctx=512, mem=256 << 20), seed=1, device=torch.device("cuda"))
+    eng.put([1], [torch.randint(0, spec.vocab, (20, ))], capture_latents=False)
+    old = gc.get_threshold()
+    gc.set_threshold(1, 1, 1)    # a full collection at (almost) every allocation: certain to fire inside the capture window
+    try:
+        for _ in range(5):
+            out, _ = eng.put([1], [torch.tensor([3])], capture_latents=False)
+    finally:
+        gc.set_threshold(*old)
+    assert eng.graph_replays >= 2 and torch.isfinite(out.float()).all()

@@ -1,5 +1,7 @@
-"""Tensor parallelism on real GPUs (needs >= 2): NCCL baseline and fused GEMM->all-reduce (symmetric memory, peer /
-multicast reductions from the GEMM epilogue) must both reproduce the single-GPU logits; HCache restore under TP."""
+"""Tensor parallelism on real GPUs (needs >= 2): the NCCL baseline and the flag-protocol collectives (GEMM tail signal,
+all-reduce / reduce-scatter + all-gather inside the norm kernel over peer or NVLS multicast addresses, all-gather -> GEMM
+waits, logits gather) must both reproduce the single-GPU logits; HCache restore (replicated and PCIe-sharded) under TP.
+The same script runs for emulated ranks on one GPU in tests/test_gpu_tp_loopback.py."""
 import pytest
 import torch
 
@@ -11,7 +13,10 @@ ARCH = dict(model_type="llama", n_layers=3, hidden=1024, n_heads=8, n_kv_heads=8
             norm="rms", act="silu", gated_mlp=True, pos_emb="rope", max_positions=2048)
 
 
-def _rank_fn(rank, world, arch_kwargs, fused, seed):
+def _rank_fn(rank, world, arch_kwargs, fused, seed, nvls=True):
+    import os
+    os.environ["HDS_TP_NVLS"] = "1" if nvls else "0"
+    os.environ["HDS_TP_STRICT"] = "1"     # a missing symmetric-memory set-up must fail the test, not fall back to NCCL
     import torch
     import torch.distributed as dist
     from hcache_deepspeed_b200.inference.v2 import RaggedInferenceEngineConfig
@@ -54,10 +59,13 @@ def _rank_fn(rank, world, arch_kwargs, fused, seed):
     logits, lat = eng.put([1, 2], [a, b])
     outs = [logits.float().cpu()]
     cur = logits.argmax(-1).cpu()
-    for _ in range(3):
+    for _ in range(5):                     # the last steps replay the decode CUDA graph (flag waits inside the graph)
         lg, _ = eng.put([1, 2], [cur[0:1], cur[1:2]], capture_latents=False)
         outs.append(lg.float().cpu())
         cur = lg.argmax(-1).cpu()
+    mid = torch.randint(0, spec.vocab, (40, ), generator=g)   # fp32 partial sums + reduce-scatter / all-gather
+    lg, _ = eng.put([1], [mid], capture_latents=False)
+    outs.append(lg.float().cpu())
     if world > 1:
         objs = [lat[0]] if rank == 0 else [None]
         dist.broadcast_object_list(objs, src=0)
@@ -79,19 +87,24 @@ def _rank_fn(rank, world, arch_kwargs, fused, seed):
             # fp32 reductions land in arrival order: equal up to rounding, not bit for bit
             torch.testing.assert_close(lc.float().cpu(), outs[-1], rtol=3e-2, atol=3e-2)
     torch.cuda.synchronize()
-    return outs, used_fused
+    nvls_used = bool(getattr(eng.model().comm, "use_nvls", False))
+    if world > 1:
+        dist.barrier()
+    return outs, used_fused, nvls_used
 
 
-@pytest.mark.parametrize("fused", [False, True])
-def test_tp2_matches_single_gpu(fused):
-    if torch.cuda.device_count() < 2:
-        pytest.skip("needs 2 GPUs")
-    single, _ = run_distributed(_rank_fn, 1, ARCH, False, 5)[0]
-    multi = run_distributed(_rank_fn, 2, ARCH, fused, 5)
-    for r in range(2):
-        outs, used_fused = multi[r]
+@pytest.mark.parametrize("world,fused,nvls", [(2, False, True), (2, True, True), (2, True, False), (4, True, True), (8, True, True),
+                                              (8, True, False)])
+def test_tp_matches_single_gpu(world, fused, nvls):
+    if torch.cuda.device_count() < world:
+        pytest.skip(f"needs {world} GPUs")
+    single = run_distributed(_rank_fn, 1, ARCH, False, 5)[0][0]
+    multi = run_distributed(_rank_fn, world, ARCH, fused, 5, nvls, timeout=600.0)
+    for r in range(world):
+        outs, used_fused, nvls_used = multi[r]
         if fused:
             assert used_fused, "fused collectives silently fell back to NCCL"
         for want, got in zip(single, outs):
             torch.testing.assert_close(got, want, rtol=6e-2, atol=6e-2)
-    torch.testing.assert_close(multi[0][0][0], multi[1][0][0], rtol=2e-2, atol=2e-2)  # ranks agree up to reduction order
+    print(f"tp{world} fused={fused} nvls requested={nvls} used={multi[0][2]}: logits match the single-GPU engine")
+    torch.testing.assert_close(multi[0][0][0], multi[world - 1][0][0], rtol=2e-2, atol=2e-2)  # ranks agree up to reduction order
