@@ -18,7 +18,6 @@ from ....models import families
 from ....models.arch import ArchSpec, arch_from_hf_config, supported_model_types
 from ....models.flat_model import (make_metadata_filename, make_model_config_filename, make_param_filename,
                                    restore_model_weights)
-from ....models.transformer import RaggedTransformer, TPComm
 from ....models.weights import load_weights, random_weights
 
 POLICIES = {}
@@ -61,7 +60,8 @@ class InferenceV2Policy:
             return dt
         return torch.bfloat16
 
-    def build_model(self, engine_config, mp_group) -> RaggedTransformer:
+    def build_model(self, engine_config, mp_group) -> "RaggedTransformer":
+        from ....models.transformer import RaggedTransformer, TPComm  # deferred: the executor imports this package's parent
         tp_size = engine_config.tensor_parallel.tp_size
         tp_rank = 0
         if tp_size > 1:

@@ -172,12 +172,12 @@ class CudaOps:
             comm.pre_wait()
             kw = {}
             if scatter_rows is not None:
-                mc = comm.multicast_ptr(out)
-                kw = dict(row0=scatter_rows[0], n_rows=scatter_rows[1], signal=True, out_mc=mc,
+                mc = comm.multicast_ptr(out, "st")
+                kw = dict(row0=scatter_rows[0], n_rows=scatter_rows[1], signal=not comm.debug_nosync, out_mc=mc,
                           out_ptrs=None if mc else comm.peer_ptrs_raw(out))
-            return self.k.norm_tp(comm.ctx, x, gamma, out, comm.peer_ptrs_raw(delta), src_mc=comm.multicast_ptr(delta),
+            return self.k.norm_tp(comm.ctx, x, gamma, out, comm.peer_ptrs_raw(delta), src_mc=comm.multicast_ptr(delta, "ld"),
                                   partial_16bit=delta.dtype != torch.float32, zero_buf=zero_buf, beta=beta, res_out=res_out,
-                                  eps=eps, layer_norm=layer_norm, **kw)
+                                  eps=eps, layer_norm=layer_norm, wait=not comm.debug_nosync, **kw)
         return self.k.norm(x, gamma, out, beta=beta, delta=delta, zero_delta=zero_delta, res_out=res_out, eps=eps,
                            layer_norm=layer_norm)
 

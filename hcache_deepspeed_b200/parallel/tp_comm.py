@@ -86,10 +86,16 @@ class FlagTPComm(TPComm):
         i, off = self._locate(t)
         return [b + off + byte_offset for b in self._peer_bases[i]]
 
-    def multicast_ptr(self, t: torch.Tensor) -> Optional[int]:
-        """NVLS alias of ``t`` (``multimem.*`` address) or None."""
+    #: which halves of the NVLS path are in use (``HDS_TP_NVLS_LD`` / ``HDS_TP_NVLS_ST`` = 0 switch one off for experiments)
+    nvls_ld = True
+    nvls_st = True
+
+    def multicast_ptr(self, t: torch.Tensor, kind: str = "ld") -> Optional[int]:
+        """NVLS alias of ``t`` (``multimem.*`` address) or None. ``kind``: "ld" (``multimem.ld_reduce`` source) or "st"
+        (``multimem.st`` destination)."""
         i, off = self._locate(t)
-        return self._mc_bases[i] + off if self._mc_bases[i] and self.use_nvls else None
+        on = self.use_nvls and (self.nvls_ld if kind == "ld" else self.nvls_st)
+        return self._mc_bases[i] + off if self._mc_bases[i] and on else None
 
     # ---- protocol -----------------------------------------------------------------------------------------
     def _make_ctx(self) -> None:
@@ -110,9 +116,15 @@ class FlagTPComm(TPComm):
         except Exception:
             pass
 
+    #: experiments only (tools/tp_decode_probe.py): drop every wait and signal — results are WRONG, timing shows what the
+    #: flag exchanges cost
+    debug_nosync = False
+
     def arm(self, wait: bool = False, signal: bool = False) -> None:
         """Attach a flag wait / signal to the next GEMM-family launch of this thread."""
         from ..ops import kernels
+        if self.debug_nosync:
+            return
         if kernels.tp_disarm():
             raise RuntimeError("a tensor-parallel wait/signal was armed but the launch that should carry it never happened")
         if wait:
@@ -121,10 +133,14 @@ class FlagTPComm(TPComm):
 
     def signal(self) -> None:
         from ..ops import kernels
+        if self.debug_nosync:
+            return
         kernels.tp_signal(self.ctx)
 
     def wait(self) -> None:
         from ..ops import kernels
+        if self.debug_nosync:
+            return
         self.pre_wait()
         kernels.tp_wait(self.ctx)
 
@@ -142,7 +158,7 @@ class FlagTPComm(TPComm):
         from ..ops import kernels
         self.pre_wait()
         kernels.tp_gather_cols(self.ctx, out_full, self.peer_ptrs_raw(local), local.stride(0), [a for a, _ in vocab_ranges],
-                               [b - a for a, b in vocab_ranges], local.shape[0], wait=True)
+                               [b - a for a, b in vocab_ranges], local.shape[0], wait=not self.debug_nosync)
         return out_full
 
 
@@ -161,6 +177,8 @@ class FusedTPComm(FlagTPComm):
         except Exception:
             pass
         self.use_nvls = os.environ.get("HDS_TP_NVLS", "1") != "0"
+        self.nvls_ld = os.environ.get("HDS_TP_NVLS_LD", "1") != "0"
+        self.nvls_st = os.environ.get("HDS_TP_NVLS_ST", "1") != "0"
         self._make_ctx()
         self.use_nvls = self.use_nvls and bool(self._mc_bases[0])
         logger.info(f"TP rank {self.rank}/{self.size}: flag protocol ready ({'NVLS multimem' if self.use_nvls else 'peer loads/stores'})")

@@ -58,11 +58,12 @@ def _rank_fn(rank, world, arch_kwargs, fused, seed, nvls=True):
     a, b = torch.randint(0, spec.vocab, (300, ), generator=g), torch.randint(0, spec.vocab, (40, ), generator=g)
     logits, lat = eng.put([1, 2], [a, b])
     outs = [logits.float().cpu()]
-    cur = logits.argmax(-1).cpu()
-    for _ in range(5):                     # the last steps replay the decode CUDA graph (flag waits inside the graph)
+    # decode inputs are fixed tokens, not each run's own arg-max: with random weights the top logits are nearly tied
+    # and a rounding-level difference would otherwise send the runs down different token paths
+    for step in range(5):
+        cur = torch.randint(0, spec.vocab, (2, ), generator=g)                     # the last steps replay the decode CUDA graph (flag waits inside the graph)
         lg, _ = eng.put([1, 2], [cur[0:1], cur[1:2]], capture_latents=False)
         outs.append(lg.float().cpu())
-        cur = lg.argmax(-1).cpu()
     mid = torch.randint(0, spec.vocab, (40, ), generator=g)   # fp32 partial sums + reduce-scatter / all-gather
     lg, _ = eng.put([1], [mid], capture_latents=False)
     outs.append(lg.float().cpu())

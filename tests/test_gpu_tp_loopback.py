@@ -61,11 +61,12 @@ def _script(eng, spec, rank, world, comm, shared):
     a, b = torch.randint(0, spec.vocab, (300, ), generator=g), torch.randint(0, spec.vocab, (40, ), generator=g)
     logits, lat = eng.put([1, 2], [a, b])
     outs = [logits.float().cpu()]
-    cur = logits.argmax(-1).cpu()
-    for _ in range(3):
+    # decode inputs are fixed tokens, not each run's own arg-max: with random weights the top logits are nearly tied
+    # and a rounding-level difference would otherwise send the runs down different token paths
+    for step in range(3):
+        cur = torch.randint(0, spec.vocab, (2, ), generator=g)
         lg, _ = eng.put([1, 2], [cur[0:1], cur[1:2]], capture_latents=False)
         outs.append(lg.float().cpu())
-        cur = lg.argmax(-1).cpu()
     mid = torch.randint(0, spec.vocab, (40, ), generator=g)
     lg, _ = eng.put([1], [mid], capture_latents=False)
     outs.append(lg.float().cpu())
