@@ -133,20 +133,26 @@ def run_ours(a):
     if tp > 1 and os.environ.get("HDS_TP_STRICT") == "1":
         assert getattr(model.comm, "fused", False), "tensor-parallel run without the fused flag-protocol collectives"
 
-    # synthetic host-DRAM hidden-state cache: one pinned [L, ctx, H] tensor (every session H2Ds its own copy)
+    # synthetic host-DRAM hidden-state cache: one pinned [L, ctx, H] tensor (every session H2Ds its own copy). Tensor
+    # parallel: every rank keeps (and transfers) only its 1/tp row slice of the hidden states; the restore kernels gather
+    # the slices from peer HBM over NVLink — so only that slice is ever allocated (a 70B / 16K-token cache is 21 GB)
     g = torch.Generator().manual_seed(7)
-    latents = torch.empty((spec.n_layers, ctx, spec.hidden), dtype=torch.bfloat16, pin_memory=True)
-    latents.copy_((torch.randn(latents.shape, generator=g) * 0.5).to(torch.bfloat16))
+    sharded = tp > 1 and bool(getattr(model.comm, "fused", False))
+    lo, hi = eng.latent_row_range(ctx) if sharded else (0, ctx)
+    latents = torch.empty((spec.n_layers, hi - lo, spec.hidden), dtype=torch.bfloat16, pin_memory=True)
+    for l in range(spec.n_layers):   # layer by layer: the fp32 staging of a whole 70B cache would not fit comfortably
+        latents[l].copy_((torch.randn((hi - lo, spec.hidden), generator=g) * 0.5).to(torch.bfloat16))
+    lat_slice = latents
     ctx_tokens = torch.randint(0, spec.vocab, (ctx, ), generator=g).pin_memory()
     new_tokens = [torch.randint(0, spec.vocab, (n_new, ), generator=g).pin_memory() for _ in range(B)]
     from hcache_deepspeed_b200.hcache import LinkModel, plan_restore
     # measured input of the planner: how long the new turn's prefill occupies the GPU (it shares the restore window)
-    eng.restore_kv([10 ** 9], [ctx_tokens], [latents], do_checks=False, defer=False)
+    eng.restore_kv([10 ** 9], [ctx_tokens], [latents], do_checks=False, defer=False, sharded=sharded)
     torch.cuda.synchronize()
     p0, p1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     eng.put([10 ** 9], [new_tokens[0]], do_checks=False)
     eng.flush(10 ** 9)
-    eng.restore_kv([10 ** 9], [ctx_tokens], [latents], do_checks=False, defer=False)
+    eng.restore_kv([10 ** 9], [ctx_tokens], [latents], do_checks=False, defer=False, sharded=sharded)
     torch.cuda.synchronize()
     p0.record()
     eng.put([10 ** 9], [new_tokens[0]], do_checks=False)
@@ -186,13 +192,7 @@ def run_ours(a):
                 "layer_bytes": lat_hidden[0].numel() * 2}
         for l in range(lat_hidden.shape[0]):
             nvme["h"].sync_pwrite(lat_hidden[l], nvme["path"], l * nvme["layer_bytes"])
-    # tensor parallel: every rank keeps (and transfers) only its 1/tp row slice of the hidden states; the restore
-    # kernels gather the slices from peer HBM over NVLink (needs the fused/symmetric-memory communicator)
-    sharded = tp > 1 and bool(getattr(model.comm, "fused", False))
-    if sharded:
-        lo, hi = eng.latent_row_range(ctx)
-        lat_slice = latents[:, lo:hi].contiguous().pin_memory()
-    rows_moved = (hi - lo) if sharded else ctx
+    rows_moved = hi - lo
     h2d_step = B * (len(hidden_layers) * rows_moved * spec.hidden * 2 + ctx * 4 + n_new * 4) + B * D * 4 + \
         B * (kv_pages.numel() * 2 if kv_pages is not None else 0)
     d2h_step = B * (D + 1) * 4

@@ -92,7 +92,7 @@ class InferenceV2Policy:
             comm = make_tp_comm(mp_group, tp_size, tp_rank, device)
         model = RaggedTransformer(self.arch, weights, engine_config.state_manager, dtype=dtype, device=device,
                                   tp_rank=tp_rank, tp_size=tp_size, comm=comm,
-                                  capture_latents=engine_config.hcache.enabled)
+                                  capture_latents=engine_config.hcache.enabled and engine_config.hcache.capture != "off")
         mode = getattr(getattr(engine_config, "quantization", None), "quantization_mode", None)
         if mode == "wf8af8":
             model.quantize_weights_fp8()

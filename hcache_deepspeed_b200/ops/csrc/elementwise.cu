@@ -204,53 +204,80 @@ struct TpReduce {
     TpSync sync;
 };
 
-template <int VPT, bool kBf16, bool kLayerNorm, bool kPartial16>
-__global__ void __launch_bounds__(kNormThreads)
+template <int THREADS>
+__device__ __forceinline__ float block_sum_n(float v, float* red) {
+    v = warp_sum(v);
+    const int w = threadIdx.x >> 5, l = threadIdx.x & 31;
+    if (l == 0) red[w] = v;
+    __syncthreads();
+    float t = (l < (THREADS / 32)) ? red[l] : 0.0f;
+    t = warp_sum(t);
+    __syncthreads();
+    return t;
+}
+
+template <bool kBf16>
+__device__ __forceinline__ void add_h8(float (&v)[8], const uint4& d) {
+    v[0] += unpack_lo<kBf16>(d.x); v[1] += unpack_hi<kBf16>(d.x);
+    v[2] += unpack_lo<kBf16>(d.y); v[3] += unpack_hi<kBf16>(d.y);
+    v[4] += unpack_lo<kBf16>(d.z); v[5] += unpack_hi<kBf16>(d.z);
+    v[6] += unpack_lo<kBf16>(d.w); v[7] += unpack_hi<kBf16>(d.w);
+}
+
+// One CTA per row, THREADS x VPT 16-byte vectors per row (VPT is 1 up to hidden size 8192: with a remote round trip of
+// a few microseconds per load the row must be fetched by ONE wave of loads, all issued before the first is consumed).
+template <int THREADS, int VPT, bool kBf16, bool kLayerNorm, bool kPartial16>
+__global__ void __launch_bounds__(THREADS)
 norm_tp_kernel(const void* __restrict__ x_in, void* res_out, void* __restrict__ out, const void* __restrict__ gamma,
                const void* __restrict__ beta, int cols, float eps, int64_t ld_in, int64_t ld_out, const TpReduce tp) {
-    __shared__ float red[kNormThreads / 32];
+    __shared__ float red[32];
     pdl_enter();
-    if (tp.sync.wait) tp_wait_cta(tp.sync);
     const int nvec = cols >> 3;
     const bool live = static_cast<int>(blockIdx.x) < tp.n_rows;
     const int r = tp.row0 + blockIdx.x;
+    // the local operands first: their latency hides behind the flag wait
+    uint4 xq[VPT];
+    if (live) {
+        const char* xrow = reinterpret_cast<const char*>(x_in) + static_cast<int64_t>(r) * ld_in * 2;
+#pragma unroll
+        for (int i = 0; i < VPT; ++i) {
+            const int vi = threadIdx.x + i * THREADS;
+            if (vi < nvec) xq[i] = *reinterpret_cast<const uint4*>(xrow + vi * 16);
+        }
+    }
+    if (tp.sync.wait) tp_wait_cta(tp.sync);
     if (tp.zero_buf != nullptr) {
         // all-reduce shape: CTA r clears row r; scatter shape: the CTAs of this launch share all rows_total rows
         const int step = tp.scatter ? static_cast<int>(gridDim.x) : tp.rows_total;
         for (int rr = tp.scatter ? static_cast<int>(blockIdx.x) : r; rr < tp.rows_total; rr += step) {
             float4* zp = reinterpret_cast<float4*>(tp.zero_buf + static_cast<int64_t>(rr) * cols);
-            for (int vi = threadIdx.x; vi < 2 * nvec; vi += kNormThreads) zp[vi] = make_float4(0.f, 0.f, 0.f, 0.f);
+            for (int vi = threadIdx.x; vi < 2 * nvec; vi += THREADS) zp[vi] = make_float4(0.f, 0.f, 0.f, 0.f);
         }
     }
     float v[VPT][8];
     float sum = 0.0f, sumsq = 0.0f;
     if (live) {
-        const char* xrow = reinterpret_cast<const char*>(x_in) + static_cast<int64_t>(r) * ld_in * 2;
 #pragma unroll
         for (int i = 0; i < VPT; ++i) {
-            const int vi = threadIdx.x + i * kNormThreads;
+            const int vi = threadIdx.x + i * THREADS;
             if (vi < nvec) {
-                const uint4 q = *reinterpret_cast<const uint4*>(xrow + vi * 16);
-                v[i][0] = unpack_lo<kBf16>(q.x); v[i][1] = unpack_hi<kBf16>(q.x);
-                v[i][2] = unpack_lo<kBf16>(q.y); v[i][3] = unpack_hi<kBf16>(q.y);
-                v[i][4] = unpack_lo<kBf16>(q.z); v[i][5] = unpack_hi<kBf16>(q.z);
-                v[i][6] = unpack_lo<kBf16>(q.w); v[i][7] = unpack_hi<kBf16>(q.w);
+                v[i][0] = unpack_lo<kBf16>(xq[i].x); v[i][1] = unpack_hi<kBf16>(xq[i].x);
+                v[i][2] = unpack_lo<kBf16>(xq[i].y); v[i][3] = unpack_hi<kBf16>(xq[i].y);
+                v[i][4] = unpack_lo<kBf16>(xq[i].z); v[i][5] = unpack_hi<kBf16>(xq[i].z);
+                v[i][6] = unpack_lo<kBf16>(xq[i].w); v[i][7] = unpack_hi<kBf16>(xq[i].w);
                 const int64_t e = static_cast<int64_t>(r) * cols + vi * 8;  // element offset in a partial-sum buffer
                 if constexpr (kPartial16) {
                     if (tp.src_mc != nullptr) {
                         const uint4 d = multimem_ld_reduce_v4_h2<kBf16>(tp.src_mc + e * 2);
-                        v[i][0] += unpack_lo<kBf16>(d.x); v[i][1] += unpack_hi<kBf16>(d.x);
-                        v[i][2] += unpack_lo<kBf16>(d.y); v[i][3] += unpack_hi<kBf16>(d.y);
-                        v[i][4] += unpack_lo<kBf16>(d.z); v[i][5] += unpack_hi<kBf16>(d.z);
-                        v[i][6] += unpack_lo<kBf16>(d.w); v[i][7] += unpack_hi<kBf16>(d.w);
+                        add_h8<kBf16>(v[i], d);
                     } else {
-                        for (int s = 0; s < tp.n; ++s) {
-                            const uint4 d = ld_relaxed_sys_v4(tp.src[s] + e * 2);
-                            v[i][0] += unpack_lo<kBf16>(d.x); v[i][1] += unpack_hi<kBf16>(d.x);
-                            v[i][2] += unpack_lo<kBf16>(d.y); v[i][3] += unpack_hi<kBf16>(d.y);
-                            v[i][4] += unpack_lo<kBf16>(d.z); v[i][5] += unpack_hi<kBf16>(d.z);
-                            v[i][6] += unpack_lo<kBf16>(d.w); v[i][7] += unpack_hi<kBf16>(d.w);
-                        }
+                        uint4 d[kTpMaxRanks];
+#pragma unroll
+                        for (int s = 0; s < kTpMaxRanks; ++s)
+                            if (s < tp.n) d[s] = ld_relaxed_sys_v4(tp.src[s] + e * 2);
+#pragma unroll
+                        for (int s = 0; s < kTpMaxRanks; ++s)
+                            if (s < tp.n) add_h8<kBf16>(v[i], d[s]);
                     }
                 } else {
                     if (tp.src_mc != nullptr) {
@@ -259,13 +286,24 @@ norm_tp_kernel(const void* __restrict__ x_in, void* res_out, void* __restrict__ 
                         v[i][0] += d0.x; v[i][1] += d0.y; v[i][2] += d0.z; v[i][3] += d0.w;
                         v[i][4] += d1.x; v[i][5] += d1.y; v[i][6] += d1.z; v[i][7] += d1.w;
                     } else {
-                        for (int s = 0; s < tp.n; ++s) {
-                            const uint4 a = ld_relaxed_sys_v4(tp.src[s] + e * 4);
-                            const uint4 b = ld_relaxed_sys_v4(tp.src[s] + e * 4 + 16);
-                            v[i][0] += __uint_as_float(a.x); v[i][1] += __uint_as_float(a.y);
-                            v[i][2] += __uint_as_float(a.z); v[i][3] += __uint_as_float(a.w);
-                            v[i][4] += __uint_as_float(b.x); v[i][5] += __uint_as_float(b.y);
-                            v[i][6] += __uint_as_float(b.z); v[i][7] += __uint_as_float(b.w);
+#pragma unroll
+                        for (int s0 = 0; s0 < kTpMaxRanks; s0 += 4) {   // four ranks' loads in flight at a time
+                            if (s0 >= tp.n) break;
+                            uint4 a[4], b[4];
+#pragma unroll
+                            for (int j = 0; j < 4; ++j)
+                                if (s0 + j < tp.n) {
+                                    a[j] = ld_relaxed_sys_v4(tp.src[s0 + j] + e * 4);
+                                    b[j] = ld_relaxed_sys_v4(tp.src[s0 + j] + e * 4 + 16);
+                                }
+#pragma unroll
+                            for (int j = 0; j < 4; ++j)
+                                if (s0 + j < tp.n) {
+                                    v[i][0] += __uint_as_float(a[j].x); v[i][1] += __uint_as_float(a[j].y);
+                                    v[i][2] += __uint_as_float(a[j].z); v[i][3] += __uint_as_float(a[j].w);
+                                    v[i][4] += __uint_as_float(b[j].x); v[i][5] += __uint_as_float(b[j].y);
+                                    v[i][6] += __uint_as_float(b[j].z); v[i][7] += __uint_as_float(b[j].w);
+                                }
                         }
                     }
                 }
@@ -292,13 +330,13 @@ norm_tp_kernel(const void* __restrict__ x_in, void* res_out, void* __restrict__ 
     }
     float mean = 0.0f, rstd;
     if (kLayerNorm) {
-        sum = block_sum_256(sum, red);
+        sum = block_sum_n<THREADS>(sum, red);
         mean = sum / cols;
         float var = 0.0f;
         if (live) {
 #pragma unroll
             for (int i = 0; i < VPT; ++i) {
-                const int vi = threadIdx.x + i * kNormThreads;
+                const int vi = threadIdx.x + i * THREADS;
                 if (vi < nvec) {
 #pragma unroll
                     for (int j = 0; j < 8; ++j) {
@@ -308,16 +346,16 @@ norm_tp_kernel(const void* __restrict__ x_in, void* res_out, void* __restrict__ 
                 }
             }
         }
-        var = block_sum_256(var, red);
+        var = block_sum_n<THREADS>(var, red);
         rstd = rsqrtf(var / cols + eps);
     } else {
-        sumsq = block_sum_256(sumsq, red);
+        sumsq = block_sum_n<THREADS>(sumsq, red);
         rstd = rsqrtf(sumsq / cols + eps);
     }
     if (live) {
 #pragma unroll
         for (int i = 0; i < VPT; ++i) {
-            const int vi = threadIdx.x + i * kNormThreads;
+            const int vi = threadIdx.x + i * THREADS;
             if (vi < nvec) {
                 const uint4 g = *reinterpret_cast<const uint4*>(reinterpret_cast<const char*>(gamma) + vi * 16);
                 const float gg[8] = {unpack_lo<kBf16>(g.x), unpack_hi<kBf16>(g.x), unpack_lo<kBf16>(g.y), unpack_hi<kBf16>(g.y),
@@ -347,21 +385,20 @@ norm_tp_kernel(const void* __restrict__ x_in, void* res_out, void* __restrict__ 
             }
         }
     }
-    if (tp.sync.signal) tp_signal_tail(tp.sync, gridDim.x);
+    if (tp.sync.signal) tp_signal_tail<true>(tp.sync, gridDim.x);
 }
 
 template <bool kBf16, bool kLayerNorm, bool kPartial16>
 static int launch_norm_tp_vpt(int grid, int cols, const void* x, void* res_out, void* out, const void* gamma, const void* beta,
                               float eps, int64_t ld_in, int64_t ld_out, const TpReduce& tp, cudaStream_t s) {
     const int nvec = cols / 8;
-    const int vpt = (nvec + kNormThreads - 1) / kNormThreads;
-#define HDS_NORM_TP_LAUNCH(V)                                                                                       \
-    launch_kernel(norm_tp_kernel<V, kBf16, kLayerNorm, kPartial16>, dim3(grid), dim3(kNormThreads), 0, s, x, res_out, \
-                  out, gamma, beta, cols, eps, ld_in, ld_out, tp)
-    if (vpt <= 1) HDS_NORM_TP_LAUNCH(1);
-    else if (vpt <= 2) HDS_NORM_TP_LAUNCH(2);
-    else if (vpt <= 4) HDS_NORM_TP_LAUNCH(4);
-    else if (vpt <= 8) HDS_NORM_TP_LAUNCH(8);
+#define HDS_NORM_TP_LAUNCH(TH, V)                                                                                     \
+    launch_kernel(norm_tp_kernel<TH, V, kBf16, kLayerNorm, kPartial16>, dim3(grid), dim3(TH), 0, s, x, res_out, out, \
+                  gamma, beta, cols, eps, ld_in, ld_out, tp)
+    if (nvec <= 256) HDS_NORM_TP_LAUNCH(256, 1);
+    else if (nvec <= 512) HDS_NORM_TP_LAUNCH(512, 1);
+    else if (nvec <= 1024) HDS_NORM_TP_LAUNCH(1024, 1);
+    else if (nvec <= 2048) HDS_NORM_TP_LAUNCH(1024, 2);
     else {
         set_error("norm_tp: cols > 16384 unsupported");
         return HDS_ERR_UNSUPPORTED;

@@ -43,7 +43,8 @@ struct SkinnyArgs {
     int32_t* tickets;   // [n_tiles * 4], zero between calls
     const float* a_scale;  // fp8 operands only: per-token scales [M]
     const float* w_scale;  // fp8 operands only: per-feature scales [N]
-    TpSync sync;           // tensor parallel: the last CTA to retire releases the output to the peers (sync.signal)
+    TpSync sync;           // tensor parallel: the producer acquires the peers' flags before its first activation load
+                           // (sync.wait); the last CTA to retire releases the output to the peers (sync.signal)
 };
 
 template <int NT>
@@ -157,6 +158,10 @@ gemm_skinny_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_cons
                             kEvictFirst);
             }
             griddep_wait();
+            if (args.sync.wait) {  // tensor parallel: the activations were all-gathered into this buffer by the peers
+                tp_wait_thread(args.sync);
+                fence_proxy_async_global();
+            }
             for (int i = 0; i < pre; ++i)
                 tma_load_2d(smem_x + i * X_BYTES, &tmap_x, &full_bar[i], (kb0 + i) * KB, 0, kEvictLast);
             uint32_t stage = 0, phase = 1;  // the ring has been filled once

@@ -413,11 +413,18 @@ __device__ __forceinline__ void tp_wait_thread(const TpSync& s) {
         if (r != s.rank) tp_poll(s.pad[s.rank] + r, target);
 }
 // Every thread of every CTA calls this once, after the CTA's last global write (it contains a __syncthreads).
+// Thread 0 fences on behalf of the CTA (the barrier puts the other threads' writes before the fence; fences are
+// cumulative) — at GPU scope when the kernel wrote only this GPU's memory, at system scope when it stored into peers
+// (kRemoteWrites) — and takes the CTA's ticket; the last CTA of the grid issues one system-scope fence and publishes the
+// new signal count to every peer with release stores. (A system-scope fence costs several microseconds on this
+// machine: one per grid instead of one per CTA is 0.4 ms per 7B decode iteration.)
+template <bool kRemoteWrites = false>
 __device__ __forceinline__ void tp_signal_tail(const TpSync& s, uint32_t n_ctas) {
     __syncthreads();
     if (threadIdx.x == 0) {
         uint32_t* mine = s.pad[s.rank];
-        __threadfence_system();
+        if constexpr (kRemoteWrites) __threadfence_system();
+        else __threadfence();
         if (atomicAdd(mine + kTpTicket, 1u) == n_ctas - 1) {
             __threadfence_system();
             const uint32_t v = ld_acquire_gpu_u32(mine + kTpSent) + 1;
