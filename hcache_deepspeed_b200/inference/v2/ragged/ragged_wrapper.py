@@ -63,6 +63,7 @@ class RaggedBatchWrapper:
             self._off[name] = (off, n)
             off += n
         self._host = pinned_zeros((off, ), torch.int32)
+        self._host_np = self._host.numpy()   # same memory: scalar / slice writes without tensor-op dispatch overhead
         self._dev = self._host if self._device.type == "cpu" else torch.zeros(off, dtype=torch.int32,
                                                                                device=self._device)
 
@@ -82,8 +83,15 @@ class RaggedBatchWrapper:
                 raise RuntimeError(f"Ragged batch is full: {self._n_tokens} + {n} tokens exceeds {self._T}")
             if self._n_seqs >= self._S:
                 raise RuntimeError(f"Ragged batch is full: sequence limit {self._S} reached")
-        ids_off = self._off["ids"][0]
-        self._host[ids_off + self._n_tokens:ids_off + self._n_tokens + n] = tokens.reshape(-1).to(torch.int32)
+        start = self._off["ids"][0] + self._n_tokens
+        if tokens.device.type == "cpu":
+            # host tokens (the normal case): numpy view of the pinned staging buffer, ~1 us instead of ~10 us per sequence
+            if n == 1:
+                self._host_np[start] = tokens.item()
+            else:
+                self._host_np[start:start + n] = tokens.reshape(-1).numpy()
+        else:
+            self._host[start:start + n] = tokens.reshape(-1).to(torch.int32)
         s = self._seqs[self._n_seqs]
         s.n_new = n
         s.seen = seq_descriptor.seen_tokens

@@ -256,6 +256,9 @@ class RaggedTransformer:
         return (-sequence.seen_tokens) % self.kv_block_size
 
     def maybe_allocate_kv(self, sequence, n_new_tokens: int) -> None:
+        need = ceil_div(sequence.seen_tokens + n_new_tokens, self.kv_block_size) - sequence.cur_allocated_blocks
+        if need <= 0:   # the common decode step: the current block still has room
+            return
         free = self._state_manager.free_blocks
         _, n_blocks = self.get_kv_requirements(sequence, n_new_tokens, free)
         if n_blocks > 0:
