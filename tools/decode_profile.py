@@ -17,12 +17,18 @@ ctx = int(os.environ.get("CTX", 4096))
 n_new, D = 64, int(os.environ.get("D", 4))
 layers = int(os.environ.get("LAYERS", 32))
 dev = torch.device("cuda", 0)
-spec = named_arch("llama-2-7b").scaled(n_layers=layers)
+spec = named_arch(os.environ.get("MODEL", "llama-2-7b")).scaled(n_layers=layers)
+# per-rank shapes of a tensor-parallel run on one GPU (no collectives): e.g. HEADS=4 KV_HEADS=4 INTER=1376 VOCAB=4000 B=64
+# is one rank of Llama-2-7B at TP=8 with 64 sessions
+over = {k: int(os.environ[e]) for k, e in (("n_heads", "HEADS"), ("n_kv_heads", "KV_HEADS"), ("intermediate", "INTER"),
+                                           ("vocab", "VOCAB")) if e in os.environ}
+if over:
+    spec = spec.scaled(**over)
 max_ctx = ctx + n_new + 64 + 64
 cfg = RaggedInferenceEngineConfig(state_manager={
-    "max_tracked_sequences": 32, "max_ragged_batch_size": max(ctx, B * n_new) + 64, "max_ragged_sequence_count": max(B, 8),
+    "max_tracked_sequences": max(32, 2 * B), "max_ragged_batch_size": max(ctx, B * n_new) + 64, "max_ragged_sequence_count": max(B, 8),
     "max_context": max_ctx, "memory_config": {"mode": "allocate", "size": int((B + 1) * (max_ctx + 128) * spec.kv_bytes_per_token_layer() * layers)}},
-    hcache={"enabled": True, "capture": "off"})
+    hcache={"enabled": True, "capture": "off"}, use_cuda_graph_decode=os.environ.get("GRAPH", "1") == "1")
 eng = build_engine_from_arch(spec, cfg, seed=1, device=dev)
 lat = torch.empty((layers, ctx, spec.hidden), dtype=torch.bfloat16, pin_memory=True)
 lat.copy_((torch.randn(lat.shape) * 0.5).to(torch.bfloat16))
