@@ -169,17 +169,19 @@ def run_ours(a):
         link = measure_link(dev, tp_size=tp)
         allow_recompute = link.io_bytes_per_s < 0.8 * LinkModel().io_bytes_per_s     # only when the link is contended
     # planner: hidden states vs offloaded KV pages per layer by bytes moved (GQA models: KV is smaller than the hidden state)
-    plan = plan_restore(spec, ctx, link, allow_kv=(a.plan == "planner" and tp == 1),
-                        allow_recompute=allow_recompute, extra_compute_s=prefill_s)
+    plan = plan_restore(spec, ctx, link, allow_kv=a.plan == "planner", allow_recompute=allow_recompute,
+                        extra_compute_s=prefill_s)
     hidden_layers, recompute_layers, kv_layers = plan.layers_of("hidden"), plan.layers_of("none"), plan.layers_of("kv")
     lat_hidden = latents[hidden_layers[0]:hidden_layers[-1] + 1] if hidden_layers else None  # a contiguous run of layers
     kv_pages = None
     if kv_layers:
         bs_kv = model._state_manager.kv_block_size
         n_blk = (ctx + bs_kv - 1) // bs_kv
-        kv_pages = torch.empty((len(kv_layers), n_blk, 2, spec.n_kv_heads, bs_kv, spec.head_dim), dtype=torch.bfloat16,
+        # offloaded KV pages of THIS rank's KV heads (tensor parallel: every rank reloads its own shard, no collective)
+        kv_pages = torch.empty((len(kv_layers), n_blk, 2, model.n_kv, bs_kv, spec.head_dim), dtype=torch.bfloat16,
                                pin_memory=True)
-        kv_pages.copy_((torch.randn(kv_pages.shape, generator=g) * 0.3).to(torch.bfloat16))
+        for j in range(len(kv_layers)):
+            kv_pages[j].copy_((torch.randn(kv_pages.shape[1:], generator=g) * 0.3).to(torch.bfloat16))
     interleave = plan.interleave
     nvme = None
     if a.source == "nvme" and tp == 1 and lat_hidden is not None:
@@ -212,8 +214,12 @@ def run_ours(a):
                         for l in range(lat_hidden.shape[0])]
                 for r_ in reqs:
                     nvme["h"].wait(r_)
-            if sharded:
+            if sharded and not kv_layers and not recompute_layers:
                 eng.restore_kv([uid], [ctx_tokens], [lat_slice], do_checks=False, sharded=True)
+            elif sharded:
+                eng.restore_session(uid, ctx_tokens, hidden=lat_hidden, hidden_layers=hidden_layers, kv=kv_pages,
+                                    kv_layers=kv_layers, kv_layer_major=True, recompute_layers=recompute_layers,
+                                    interleave=interleave, sharded=True)
             else:
                 eng.restore_session(uid, ctx_tokens, hidden=lat_hidden, hidden_layers=hidden_layers, kv=kv_pages,
                                     kv_layers=kv_layers, kv_layer_major=True, recompute_layers=recompute_layers,
@@ -291,9 +297,9 @@ def run_ours(a):
                        "parallelism": f"tp{tp}" if replicas == 1 else f"dp{replicas}",
                        "restored_ctx": ctx, "new_turn_tokens": n_new, "decode_steps": D, "sessions_per_gpu": a.sessions},
             "details": {"numa_bound_cpus": len(numa_cpus), "hidden_state_source": a.source if nvme is not None or a.source == "dram" else "dram",
-                        "restore_plan": {"recompute_prefix_layers": 0 if sharded else len(recompute_layers),
-                                         "hidden_state_layers": spec.n_layers if sharded else len(hidden_layers),
-                                         "kv_offload_layers": 0 if sharded else len(kv_layers), "tp_sharded_restore": sharded,
+                        "restore_plan": {"recompute_prefix_layers": len(recompute_layers),
+                                         "hidden_state_layers": len(hidden_layers),
+                                         "kv_offload_layers": len(kv_layers), "tp_sharded_restore": sharded,
                                          "host_link_GBps": round(link.io_bytes_per_s / 1e9, 1)},
                         "tp_collectives": ("flag protocol: GEMM tail signal + " + ("multimem.ld_reduce/st" if getattr(model.comm, "use_nvls", False)
                                                                                  else "peer loads/stores") + " inside the norm kernel")

@@ -159,7 +159,8 @@ class InferenceEngineV2:
     def restore_session(self, uid: int, tokens: torch.Tensor, hidden: Optional[torch.Tensor] = None,
                         hidden_layers: Sequence[int] = (), kv: Optional[torch.Tensor] = None,
                         kv_layers: Sequence[int] = (), recompute_layers: Sequence[int] = (),
-                        defer: Optional[bool] = None, interleave: float = 2.5, kv_layer_major: bool = False) -> None:
+                        defer: Optional[bool] = None, interleave: float = 2.5, kv_layer_major: bool = False,
+                        sharded: bool = False) -> None:
         """Bring one session's context back following a mixed plan (``hcache/planner.py``):
 
         * ``recompute_layers`` — must be the prefix ``0..r-1``: recomputed from ``tokens`` (uses the GPU while the
@@ -170,6 +171,8 @@ class InferenceEngineV2:
         * ``hidden_layers`` — ``hidden [len(hidden_layers), n_tokens, hidden]`` through the K/V projection kernel.
 
         ``interleave``: saved layers projected per recomputed layer (layer-forward time / per-layer transfer time).
+        ``sharded`` (tensor parallel): ``hidden`` holds only this rank's row slice (``latent_row_range``) and the
+        projection gathers the peers' slices over NVLink; ``kv`` always holds this rank's own KV heads.
         """
         tokens = tokens.reshape(-1)
         n = int(tokens.numel())
@@ -193,7 +196,7 @@ class InferenceEngineV2:
         n_hidden = len(list(hidden_layers))
         # start the host-to-device stream of the hidden states FIRST: it then runs under the recomputed prefix
         if n_hidden:
-            model.restore_kv(self._batch, [hidden], layers=list(hidden_layers), defer=True)
+            model.restore_kv(self._batch, [hidden], layers=list(hidden_layers), defer=True, sharded=sharded)
         if len(list(kv_layers)):
             model.restore_kv_pages(seq.all_block_ids, kv, list(kv_layers), defer=bool(defer) and kv_layer_major,
                                    layer_major=kv_layer_major)
