@@ -96,9 +96,12 @@ class InferenceV2Policy:
         mode = getattr(getattr(engine_config, "quantization", None), "quantization_mode", None)
         if mode == "wf8af8":
             model.quantize_weights_fp8()
+        elif mode == "wf6af16":
+            # the reference's FP6 mode (modules/implementations/linear/quantized_linear.py:96-205): here E3M2 weights are fed
+            # to the tensor cores directly (kind::f8f6f4), with activations quantised to E4M3 per token instead of kept fp16
+            model.quantize_weights_fp8("e3m2")
         elif mode is not None:
-            raise ValueError(f"quantization_mode {mode!r} is not available: use 'wf8af8' (the reference's 'wf6af16' kernel is "
-                             "sm_80-only; see DESIGN.md)")
+            raise ValueError(f"quantization_mode {mode!r} is not available: use 'wf8af8' or 'wf6af16'")
         return model
 
 

@@ -20,8 +20,7 @@ def instantiate_embed(embed_config: DSEmbeddingsConfig, engine_config=None):
 def instantiate_linear(linear_config: DSLinearConfig, engine_config=None):
     mode = getattr(getattr(engine_config, "quantization", None), "quantization_mode", None)
     if mode == "wf6af16":
-        raise NotImplementedError("wf6af16 fused linear: use hcache_deepspeed_b200.linear.QuantizedLinear (FP6 weights, "
-                                  "dequantised per call), or quantization_mode='wf8af8' for the fp8 tcgen05 linear")
+        return DSLinearRegistry.instantiate_config(ConfigBundle("fp6_tcgen05_linear", linear_config))
     if mode == "wf8af8":
         return DSLinearRegistry.instantiate_config(ConfigBundle("fp8_tcgen05_linear", linear_config))
     return DSLinearRegistry.instantiate_config(ConfigBundle("blas_fp_linear", linear_config))

@@ -124,6 +124,44 @@ class Fp8TensorCoreLinear(BlasFPLinear):
         return ref.gemm(ad, wd, bias=b, act=self.act, gated=self.gated, out_dtype=hidden_states.dtype)
 
 
+@DSLinearRegistry.register_module
+class Fp6TensorCoreLinear(BlasFPLinear):
+    """``quantization_mode = "wf6af16"``: FP6 (E3M2) weights, 0.75 byte per weight in HBM, per-output-channel scales.
+    The reference dequantises FP6 to fp16 inside an sm_80 ``mma.sync`` kernel
+    (``implementations/linear/quantized_linear.py:96-205``, ``core_ops/cuda_linear/include/kernel_matmul.cuh:21-272``);
+    on Blackwell the tensor cores take E3M2 operands natively (``tcgen05.mma.kind::f8f6f4``): the TMA unpacks the 6-bit
+    stream into shared memory (tensor-map type 16U6_ALIGN16B) and the activations are quantised to E4M3 per token, so the
+    GEMM is the fp8 kernel with a different weight format (``ops/csrc/gemm_fp8.cu``). ``in_channels`` must be a multiple
+    of 128."""
+
+    @staticmethod
+    def name():
+        return "fp6_tcgen05_linear"
+
+    @staticmethod
+    def supports_config(config: DSLinearConfig) -> bool:
+        return BlasFPLinear.supports_config(config) and config.in_channels % 128 == 0
+
+    def transform_param(self, param: torch.Tensor):
+        param = super().transform_param(param)
+        if param.dim() != 2:
+            return param  # biases stay in the activation dtype
+        from ....ops.fp8 import Fp8Weight
+        return Fp8Weight.from_tensor(param, "e3m2")
+
+    def forward(self, hidden_states: torch.Tensor, w, b: Optional[torch.Tensor] = None) -> torch.Tensor:
+        n_out = w.shape[0] // 2 if self.gated else w.shape[0]
+        if hidden_states.is_cuda:
+            from ....ops import kernels as K
+            out = torch.empty((hidden_states.shape[0], n_out), dtype=hidden_states.dtype, device=hidden_states.device)
+            aq, a_s = K.quantize_fp8_rows(hidden_states)
+            return K.gemm_fp8(aq, a_s, w.q, w.scale, out, bias=b, act=self.act, gated=self.gated, w_fmt=1)
+        amax = hidden_states.float().abs().amax(dim=1, keepdim=True)
+        a_s = torch.where(amax > 0, amax / 448.0, torch.ones_like(amax))
+        ad = (hidden_states.float() / a_s).to(torch.float8_e4m3fn).float() * a_s
+        return ref.gemm(ad, w.dequantize(), bias=b, act=self.act, gated=self.gated, out_dtype=hidden_states.dtype)
+
+
 class _PreNorm(DSPreNormBase):
     layer_norm = False
 

@@ -94,6 +94,15 @@ class AsyncIOHandle:
     def poll(self, request_id: int) -> bool:
         return self._lib.hds_aio_poll(self._h, request_id) == 1
 
+    def stats(self) -> dict:
+        """How the pieces were executed so far: through kernel AIO (``io_submit``, true device queue depth) or
+        synchronously (``pread`` / ``pwrite``: unaligned pieces, no O_DIRECT on this filesystem), and the deepest
+        in-flight queue one worker reached."""
+        import ctypes
+        out = (ctypes.c_int64 * 3)()
+        self._lib.hds_aio_stats(self._h, out)
+        return {"kernel_aio_pieces": int(out[0]), "sync_pieces": int(out[1]), "max_inflight_per_worker": int(out[2])}
+
     def pending(self) -> int:
         return int(self._lib.hds_aio_pending(self._h))
 

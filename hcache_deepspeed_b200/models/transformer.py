@@ -275,20 +275,24 @@ class RaggedTransformer:
     # ------------------------------------------------------------------------------------------------
     # W8A8 (fp8) weights
     # ------------------------------------------------------------------------------------------------
-    def quantize_weights_fp8(self) -> int:
-        """``quantization_mode = "wf8af8"``: convert every layer's QKV / attention-out / MLP weights to E4M3 with
-        per-output-channel scales (embedding, LM head and norms stay 16-bit). Returns the bytes saved."""
+    def quantize_weights_fp8(self, fmt: str = "e4m3") -> int:
+        """``quantization_mode = "wf8af8"`` (``fmt="e4m3"``) or ``"wf6af16"`` (``fmt="e3m2"``: FP6 weights, 0.75 byte each in
+        HBM): convert every layer's QKV / attention-out / MLP weights to the tensor-core float format with
+        per-output-channel scales (embedding, LM head and norms stay 16-bit); activations are quantised to E4M3 per token on
+        the fly and the GEMMs run on ``tcgen05.mma.kind::f8f6f4``. FP6 needs an input dimension that is a multiple of 128
+        (a TMA rule of the packed 6-bit type); a weight that does not qualify (odd tensor-parallel shards) stays E4M3.
+        Returns the bytes saved."""
         s = self.spec
         if s.is_moe or s.parallel_residual or (self.tp_size > 1 and not self._tp_fused):
-            raise NotImplementedError("wf8af8 covers dense, sequential-residual models (tensor parallel: with the fused "
-                                      "flag-protocol collectives; mixture-of-experts and parallel-residual blocks reduce "
-                                      "through fp32 partial sums)")
+            raise NotImplementedError("wf8af8 / wf6af16 cover dense, sequential-residual models (tensor parallel: with the "
+                                      "fused flag-protocol collectives; mixture-of-experts and parallel-residual blocks "
+                                      "reduce through fp32 partial sums)")
         saved = 0
         for lw in self.w.layers:
             for name in ("w_qkv", "w_o", "w_up", "w_down"):
                 w = getattr(lw, name)
                 if isinstance(w, torch.Tensor):
-                    q = Fp8Weight.from_tensor(w)
+                    q = Fp8Weight.from_tensor(w, fmt if w.shape[1] % 128 == 0 else "e4m3")
                     saved += w.numel() * w.element_size() - q.nbytes()
                     setattr(lw, name, q)
         ks = set()

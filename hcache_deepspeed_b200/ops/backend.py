@@ -141,7 +141,7 @@ class CudaOps:
             if tp_signal:
                 comm.arm(signal=True)
             return self.k.gemm_fp8(aq, a_s, w.q, w.scale, out, bias=bias, act=act, gated=gated,
-                                   workspace=workspace if a.shape[0] <= 64 else None)
+                                   workspace=workspace if a.shape[0] <= 64 else None, w_fmt=w.fmt_code)
         if tp_wait or tp_signal:
             comm.arm(wait=tp_wait, signal=tp_signal)
         return self.k.gemm(a, w, bias=bias, act=act, gated=gated, out=out,
@@ -157,7 +157,7 @@ class CudaOps:
             aq, a_s = self._fp8_act(a)
             if tp_signal:
                 comm.arm(signal=True)
-            self.k.gemm_fp8_accum(aq, a_s, w.q, w.scale, accum, bias=bias, out_dtype=a.dtype)
+            self.k.gemm_fp8_accum(aq, a_s, w.q, w.scale, accum, bias=bias, out_dtype=a.dtype, w_fmt=w.fmt_code)
             return
         if tp_signal:
             comm.arm(signal=True)

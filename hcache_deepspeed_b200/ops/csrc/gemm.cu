@@ -121,7 +121,7 @@ struct Operands {
 // ---- prefill-size M: CTA-pair kernel (gemm_2sm.cu) ------------------------------------------------------------
 int gemm_2sm_dispatch(const void* A, int64_t lda_bytes, const float* a_scale, const void* W, int64_t ldw_bytes,
                       const float* w_scale, int M, int N, int K, bool fp8, bool bf16, int epilogue, int act, const void* bias,
-                      void* out, int64_t ldo, int bn, cudaStream_t stream);
+                      void* out, int64_t ldo, int bn, cudaStream_t stream, int w_fmt = 0);
 int gemm_2sm_dispatch_rope(const GemmArgs& g, const void* A, int64_t lda_bytes, const void* W, int64_t ldw_bytes, bool bf16,
                            bool has_q, cudaStream_t stream);
 bool is_local_device_ptr(const void* p);

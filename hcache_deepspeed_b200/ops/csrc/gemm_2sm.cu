@@ -193,7 +193,7 @@ gemm_2sm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constan
                     const uint64_t dw = make_desc_kmajor_sw128(smem_u32(smem_w + stage * W_BYTES));
 #pragma unroll
                     for (int k = 0; k < KB_ELEMS / MMA_K; ++k)  // 32 bytes of K per instruction inside the swizzle atom
-                        umma_ss_2sm<kFp8>(d_tmem, da + 2 * k, dw + 2 * k, IDESC, (kb > 0 || k > 0) ? 1u : 0u);
+                        umma_ss_2sm<kFp8>(d_tmem, da + 2 * k, dw + 2 * k, IDESC | args.idesc_or, (kb > 0 || k > 0) ? 1u : 0u);
                     umma_commit_2sm(&empty_bar[stage], 0b11);
                     if (++stage == STAGES) {
                         stage = 0;
@@ -311,7 +311,7 @@ bool is_local_device_ptr(const void* p) {
 // Shared host path: operands are 16-bit (a_scale == nullptr) or E4M3 with row / channel scales.
 int gemm_2sm_dispatch(const void* A, int64_t lda_bytes, const float* a_scale, const void* W, int64_t ldw_bytes,
                       const float* w_scale, int M, int N, int K, bool fp8, bool bf16, int epilogue, int act, const void* bias,
-                      void* out, int64_t ldo, int bn, cudaStream_t stream) {
+                      void* out, int64_t ldo, int bn, cudaStream_t stream, int w_fmt) {
     if (bn <= 0) {
         const int64_t m_tiles = (M + 255) / 256;
         bn = m_tiles * ((N + 255) / 256) * 2 >= sm_count() ? 256 : 128;
@@ -341,7 +341,12 @@ int gemm_2sm_dispatch(const void* A, int64_t lda_bytes, const float* a_scale, co
     if (fp8) {
         rc = make_tmap_2d_8b(&ta, A, K, M, lda_bytes, 128, 128);
         if (rc) return rc;
-        rc = make_tmap_2d_8b(&tw, W, K, N, ldw_bytes, 128, bn / 2);
+        if (w_fmt == 1) {   // E3M2 weights, packed 6-bit in global memory; the weights are the MMA's B operand
+            rc = make_tmap_2d_6b(&tw, W, K, N, ldw_bytes, bn / 2);
+            fa.g.idesc_or = 4u << 10;
+        } else {
+            rc = make_tmap_2d_8b(&tw, W, K, N, ldw_bytes, 128, bn / 2);
+        }
     } else {
         rc = make_tmap_2d_16b(&ta, A, K, M, lda_bytes, 64, 128, bf16);
         if (rc) return rc;
@@ -394,5 +399,5 @@ extern "C" int hds_gemm_2sm(const void* A, int64_t lda, const void* W, int64_t l
     HDS_REQUIRE(epilogue != EPI_GATED || (N % 2 == 0), "hds_gemm_2sm: gated epilogue needs an even N");
     HDS_REQUIRE(M > 0 && N > 0 && K > 0 && K % 8 == 0, "hds_gemm_2sm: K must be a positive multiple of 8");
     return gemm_2sm_dispatch(A, lda * 2, nullptr, W, ldw * 2, nullptr, M, N, K, false, dtype == 0, epilogue, act, bias, out,
-                             ldo, bn, static_cast<cudaStream_t>(stream));
+                             ldo, bn, static_cast<cudaStream_t>(stream), 0);
 }

@@ -96,6 +96,9 @@ struct GemmArgs {
     // before its first activation load (the operand was all-gathered into this GPU's buffer by the peers' norm kernels);
     // `sync.signal` — the last CTA to retire releases this kernel's output to the peers.
     TpSync sync;
+    // kind::f8f6f4 kernels: bits OR-ed into the instruction descriptor to select a non-E4M3 weight format
+    // (E3M2 = code 4 in the operand-format field of whichever side the weights are on)
+    uint32_t idesc_or;
 };
 
 // Expert that owns the 128-row tile starting at row0 (-1: past the last expert's rows).

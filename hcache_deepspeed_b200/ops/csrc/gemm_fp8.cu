@@ -167,7 +167,7 @@ gemm_fp8_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constan
                     const uint64_t dw = make_desc_kmajor_sw128(smem_u32(smem_w + stage * W_BYTES));
 #pragma unroll
                     for (int k = 0; k < kF8BK / 32; ++k)  // 32 elements = 32 B per MMA inside the 128 B swizzle atom
-                        umma_f8_ss(d_tmem, da + 2 * k, dw + 2 * k, IDESC, (kb > 0 || k > 0) ? 1u : 0u);
+                        umma_f8_ss(d_tmem, da + 2 * k, dw + 2 * k, IDESC | args.idesc_or, (kb > 0 || k > 0) ? 1u : 0u);
                     umma_commit(&empty_bar[stage]);
                     if (++stage == STAGES) {
                         stage = 0;
@@ -256,7 +256,16 @@ namespace hds {
 // gemm_2sm.cu: CTA-pair (cta_group::2) kernel shared by the 16-bit and fp8 operand kinds
 int gemm_2sm_dispatch(const void* A, int64_t lda_bytes, const float* a_scale, const void* W, int64_t ldw_bytes,
                       const float* w_scale, int M, int N, int K, bool fp8, bool bf16, int epilogue, int act, const void* bias,
-                      void* out, int64_t ldo, int bn, cudaStream_t stream);
+                      void* out, int64_t ldo, int bn, cudaStream_t stream, int w_fmt = 0);
+
+// Weight format of the NEXT hds_gemm_fp8 / hds_gemm_fp8_skinny call of this host thread (consumed by it):
+// 0 = E4M3 bytes (default), 1 = E3M2 packed 6-bit.
+static thread_local int g_next_w_fmt = 0;
+static int take_w_fmt() {
+    const int f = g_next_w_fmt;
+    g_next_w_fmt = 0;
+    return f;
+}
 }  // namespace hds
 
 using namespace hds;
@@ -278,6 +287,12 @@ extern "C" int hds_quantize_fp8_rows(const void* x, int64_t ldx, int rows, int K
     return HDS_OK;
 }
 
+extern "C" int hds_fp8_next_weight_format(int fmt) {
+    HDS_REQUIRE(fmt == 0 || fmt == 1, "hds_fp8_next_weight_format: 0 (E4M3) or 1 (E3M2 packed 6-bit)");
+    hds::g_next_w_fmt = fmt;
+    return HDS_OK;
+}
+
 extern "C" int hds_gemm_fp8(const void* Aq, int64_t lda, const float* a_scale, const void* Wq, int64_t ldw,
                             const float* w_scale, int M, int N, int K, int out_dtype, int epilogue, int act,
                             const void* bias, void* out, int64_t ldo, int bn, void* stream) {
@@ -285,10 +300,12 @@ extern "C" int hds_gemm_fp8(const void* Aq, int64_t lda, const float* a_scale, c
     HDS_REQUIRE(out_dtype == 0 || out_dtype == 1, "hds_gemm_fp8: out dtype must be 0 (bf16) or 1 (fp16)");
     HDS_REQUIRE(epilogue != EPI_GATED || (N % 2 == 0), "hds_gemm_fp8: gated epilogue needs an even N");
     HDS_REQUIRE(M > 0 && N > 0 && K > 0 && K % 16 == 0, "hds_gemm_fp8: K must be a positive multiple of 16");
+    const int w_fmt = take_w_fmt();
+    HDS_REQUIRE(w_fmt == 0 || K % 128 == 0, "hds_gemm_fp8: 6-bit weights need K to be a multiple of 128");
     // bn: 0 = auto (CTA-pair kernel above one m-tile), 64 / 128 / 256 = single-CTA tile, 1128 / 1256 = CTA-pair tile
     if ((bn == 0 && M > 128) || bn > 1000)
         return gemm_2sm_dispatch(Aq, lda, a_scale, Wq, ldw, w_scale, M, N, K, true, out_dtype == 0, epilogue, act, bias, out,
-                                 ldo, bn > 1000 ? bn - 1000 : 0, static_cast<cudaStream_t>(stream));
+                                 ldo, bn > 1000 ? bn - 1000 : 0, static_cast<cudaStream_t>(stream), w_fmt);
     if (bn <= 0) {
         // widest tile that still gives every SM work; decode-size problems take the narrow tile for more CTAs
         const int64_t m_tiles = (M + 127) / 128;
@@ -310,7 +327,12 @@ extern "C" int hds_gemm_fp8(const void* Aq, int64_t lda, const float* a_scale, c
     CUtensorMap ta, tw;
     int rc = make_tmap_2d_8b(&ta, Aq, K, M, lda, kF8BK, 128);
     if (rc) return rc;
-    rc = make_tmap_2d_8b(&tw, Wq, K, N, ldw, kF8BK, bn);
+    if (w_fmt == 1) {   // E3M2 weights (packed 6-bit): the weights are the MMA's B operand in this kernel
+        rc = make_tmap_2d_6b(&tw, Wq, K, N, ldw, bn);
+        fa.g.idesc_or = 4u << 10;
+    } else {
+        rc = make_tmap_2d_8b(&tw, Wq, K, N, ldw, kF8BK, bn);
+    }
     if (rc) return rc;
     const int work = ((M + 127) / 128) * ((N + bn - 1) / bn);
     const int grid = work < sm_count() ? work : sm_count();
@@ -415,7 +437,15 @@ extern "C" int hds_gemm_fp8_skinny(const void* Aq, int64_t lda, const float* a_s
         a.tickets = reinterpret_cast<int32_t*>(reinterpret_cast<char*>(ws) + ws_data);
     }
     CUtensorMap tw, tx;
-    int rc = make_tmap_2d_8b(&tw, Wq, K, N, ldw, 128, kSkinnyBF);
+    const int w_fmt = take_w_fmt();
+    HDS_REQUIRE(w_fmt == 0 || K % 128 == 0, "hds_gemm_fp8_skinny: 6-bit weights need K to be a multiple of 128");
+    int rc;
+    if (w_fmt == 1) {   // E3M2 weights (packed 6-bit): the weights are the MMA's A operand in the feature-major kernel
+        rc = make_tmap_2d_6b(&tw, Wq, K, N, ldw, kSkinnyBF);
+        a.idesc_or = 4u << 7;
+    } else {
+        rc = make_tmap_2d_8b(&tw, Wq, K, N, ldw, 128, kSkinnyBF);
+    }
     if (rc) return rc;
     rc = make_tmap_2d_8b(&tx, Aq, K, M, lda, 128, nt);
     if (rc) return rc;

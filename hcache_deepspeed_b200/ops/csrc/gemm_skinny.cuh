@@ -43,6 +43,7 @@ struct SkinnyArgs {
     int32_t* tickets;   // [n_tiles * 4], zero between calls
     const float* a_scale;  // fp8 operands only: per-token scales [M]
     const float* w_scale;  // fp8 operands only: per-feature scales [N]
+    uint32_t idesc_or;     // fp8 kernels: operand-format bits for 6-bit (E3M2) weights, else 0
     TpSync sync;           // tensor parallel: the producer acquires the peers' flags before its first activation load
                            // (sync.wait); the last CTA to retire releases the output to the peers (sync.signal)
 };
@@ -187,7 +188,7 @@ gemm_skinny_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_cons
                 const uint64_t dx = make_desc_kmajor_sw128(smem_u32(smem_x + stage * X_BYTES));
 #pragma unroll
                 for (int k = 0; k < 4; ++k) {  // 32 bytes of K per instruction: 16 (16-bit) or 32 (fp8) elements
-                    if constexpr (kFp8) umma_f8_ss(tmem_base, dw + 2 * k, dx + 2 * k, IDESC, (kb > kb0 || k > 0) ? 1u : 0u);
+                    if constexpr (kFp8) umma_f8_ss(tmem_base, dw + 2 * k, dx + 2 * k, IDESC | args.idesc_or, (kb > kb0 || k > 0) ? 1u : 0u);
                     else umma_f16_ss(tmem_base, dw + 2 * k, dx + 2 * k, IDESC, (kb > kb0 || k > 0) ? 1u : 0u);
                 }
                 umma_commit(&empty_bar[stage]);

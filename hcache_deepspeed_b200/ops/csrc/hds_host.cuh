@@ -149,6 +149,38 @@ inline int make_tmap_2d_8b(CUtensorMap* map, const void* base, uint64_t inner, u
     return HDS_OK;
 }
 
+// 2D tensor of PACKED 6-bit elements (e3m2 / e2m3 weights): global memory holds 16 values in 12 bytes, no gaps; the TMA
+// unpacks every 16-value group into a 16-byte slot of shared memory (12 bytes + 4 bytes of padding), which is the layout
+// tcgen05.mma.kind::f8f6f4 reads for 6-bit operands — so HBM carries 0.75 byte per weight while a shared-memory tile row
+// stays 128 bytes for 128 elements, exactly like an fp8 tile. Rules of the format (cuTensorMapEncodeTiled): inner
+// extent a multiple of 128 elements, box inner extent exactly 128, row pitch a multiple of 32 bytes, base 32-byte aligned.
+inline int make_tmap_2d_6b(CUtensorMap* map, const void* base, uint64_t inner, uint64_t outer, uint64_t pitch_bytes,
+                           uint32_t box_outer) {
+    auto enc = tensor_map_encoder();
+    if (!enc) {
+        set_error("cuTensorMapEncodeTiled unavailable (no CUDA driver?)");
+        return HDS_ERR_DRIVER;
+    }
+    if ((reinterpret_cast<uintptr_t>(base) & 31) || (pitch_bytes & 31) || (inner & 127)) {
+        set_error("6-bit TMA operand: base 32-byte aligned, row pitch a multiple of 32 bytes, K a multiple of 128");
+        return HDS_ERR_BAD_ARG;
+    }
+    cuuint64_t gdim[2] = {inner, outer};
+    cuuint64_t gstride[1] = {pitch_bytes};
+    cuuint32_t box[2] = {128, box_outer};
+    cuuint32_t estr[2] = {1, 1};
+    CUresult r = enc(map, CU_TENSOR_MAP_DATA_TYPE_16U6_ALIGN16B, 2, const_cast<void*>(base), gdim, gstride, box, estr,
+                     CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                     CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (r != CUDA_SUCCESS) {
+        char b[160];
+        snprintf(b, sizeof(b), "cuTensorMapEncodeTiled (6-bit packed) failed: CUresult %d", (int)r);
+        set_error(b);
+        return HDS_ERR_DRIVER;
+    }
+    return HDS_OK;
+}
+
 // 3D tensor [d2, d1, d0] of 16-bit elements (d0 innermost), strides in bytes for d1 and d2.
 inline int make_tmap_3d_16b(CUtensorMap* map, const void* base, uint64_t d0, uint64_t d1, uint64_t d2,
                             uint64_t stride1_bytes, uint64_t stride2_bytes, uint32_t box0, uint32_t box1,

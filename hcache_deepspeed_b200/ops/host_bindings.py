@@ -43,6 +43,8 @@ def declare(lib: ctypes.CDLL) -> None:
     lib.hds_aio_poll.restype = I
     lib.hds_aio_pending.argtypes = [P]
     lib.hds_aio_pending.restype = I32
+    lib.hds_aio_stats.argtypes = [P, P]
+    lib.hds_aio_stats.restype = None
     lib.hds_mem_lock.argtypes = [P, L]
     lib.hds_mem_lock.restype = I
     lib.hds_mem_unlock.argtypes = [P, L]

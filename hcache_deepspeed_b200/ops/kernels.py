@@ -488,7 +488,7 @@ def quantize_fp8_rows(x: torch.Tensor, q: Optional[torch.Tensor] = None,
 
 def gemm_fp8(aq: torch.Tensor, a_scale: torch.Tensor, wq: torch.Tensor, w_scale: torch.Tensor, out: torch.Tensor,
              bias: Optional[torch.Tensor] = None, act: int = ACT_IDENTITY, gated: bool = False, bn: int = 0,
-             workspace: Optional[torch.Tensor] = None, splits: int = 0) -> torch.Tensor:
+             workspace: Optional[torch.Tensor] = None, splits: int = 0, w_fmt: int = 0) -> torch.Tensor:
     """``out = epilogue((aq @ wq.T) * a_scale[:, None] * w_scale[None, :] + bias)`` with E4M3 operands on
     ``tcgen05.mma.kind::f8f6f4`` (fp32 accumulation in TMEM). ``aq``: [M, K] uint8, ``wq``: [N, K] uint8.
     M <= 64 with ``bn == 0`` takes the feature-major weight-streaming kernel (split-K through ``workspace``, a zeroed
@@ -498,9 +498,12 @@ def gemm_fp8(aq: torch.Tensor, a_scale: torch.Tensor, wq: torch.Tensor, w_scale:
     _check_2d(out, "out")
     M, K = aq.shape
     N = wq.shape[0]
-    assert wq.shape[1] == K and aq.dtype == torch.uint8 and wq.dtype == torch.uint8
+    # w_fmt 1: E3M2 (FP6) weights packed 6 bits each — [N, 3K/4] bytes, unpacked by the TMA on the way to shared memory
+    assert wq.shape[1] == (K * 3 // 4 if w_fmt == 1 else K) and aq.dtype == torch.uint8 and wq.dtype == torch.uint8
     assert a_scale.dtype == torch.float32 and w_scale.dtype == torch.float32
     lib = native.cuda_lib()
+    if w_fmt:
+        native.check(lib.hds_fp8_next_weight_format(w_fmt), "hds_fp8_next_weight_format")
     if M <= 64 and bn == 0:
         rc = lib.hds_gemm_fp8_skinny(_p(aq), aq.stride(0), _p(a_scale), _p(wq), wq.stride(0), _p(w_scale), M, N, K, _dt(out),
                                      EPI_GATED if gated else EPI_STORE, act, _p(bias), _p(out), out.stride(0), None, 0,
@@ -521,13 +524,16 @@ def gemm_fp8_skinny_workspace_bytes(M: int, N: int) -> int:
 
 
 def gemm_fp8_accum(aq: torch.Tensor, a_scale: torch.Tensor, wq: torch.Tensor, w_scale: torch.Tensor, accum: torch.Tensor,
-                   bias: Optional[torch.Tensor] = None, out_dtype: torch.dtype = torch.bfloat16, splits: int = 0) -> torch.Tensor:
+                   bias: Optional[torch.Tensor] = None, out_dtype: torch.dtype = torch.bfloat16, splits: int = 0,
+                   w_fmt: int = 0) -> torch.Tensor:
     """``accum (fp32) += (aq @ wq.T) * scales (+ bias once)`` for M <= 64 (decode): split-K partial sums go straight
     into ``accum`` with fp32 atomics, no scratch."""
     M, K = aq.shape
     N = wq.shape[0]
     assert accum.dtype == torch.float32 and M <= 64
     dt = 0 if out_dtype == torch.bfloat16 else 1
+    if w_fmt:
+        native.check(native.cuda_lib().hds_fp8_next_weight_format(w_fmt), "hds_fp8_next_weight_format")
     rc = native.cuda_lib().hds_gemm_fp8_skinny(_p(aq), aq.stride(0), _p(a_scale), _p(wq), wq.stride(0), _p(w_scale), M, N, K, dt,
                                                2, ACT_IDENTITY, _p(bias), None, 0, _p(accum), accum.stride(0), None, 0, splits,
                                                _stream())

@@ -6,8 +6,9 @@
  *   - ragged batch builder          (ref: ragged/ragged_wrapper.py:134-218 insert_sequence/finalize python lists,
  *                                    kernels/ragged_ops/atom_builder/atom_builder.cpp:10-53)
  *   - asynchronous file I/O handle  (ref: csrc/aio/py_lib/deepspeed_py_io_handle.cpp, py_ds_aio.cpp:15-116 —
- *                                    libaio; here a thread pool over pread/pwrite with optional O_DIRECT,
- *                                    because libaio headers are not part of the target image)
+ *                                    libaio; here kernel AIO through raw io_setup / io_submit / io_getevents system
+ *                                    calls, queue_depth iocbs in flight per worker, O_DIRECT; pread / pwrite for what
+ *                                    cannot be submitted that way)
  */
 #ifndef HDS_HOST_H
 #define HDS_HOST_H
@@ -67,6 +68,9 @@ int64_t hds_aio_wait(void* h, int64_t request_id);
 /* 1 if finished, 0 if still running, negative on unknown id. Never blocks. */
 int hds_aio_poll(void* h, int64_t request_id);
 int32_t hds_aio_pending(void* h);
+/* out[0] = pieces completed through kernel AIO (io_submit), out[1] = pieces executed synchronously (pread / pwrite),
+ * out[2] = deepest in-flight queue one worker reached. */
+void hds_aio_stats(void* h, int64_t* out);
 
 /* mlock / munlock helpers for page-locked staging buffers that are not CUDA-registered. */
 int hds_mem_lock(void* ptr, int64_t nbytes);

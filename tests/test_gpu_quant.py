@@ -155,3 +155,63 @@ def test_gemm_fp8_skinny(M, mode, use_ws):
             torch.testing.assert_close(out.float(), ref_out, rtol=2e-2, atol=2e-2)
     if ws is not None:
         assert int(ws.view(torch.int32).abs().max()) == 0
+
+
+def _fp6_case(M, N, Kd, seed=0):
+    from hcache_deepspeed_b200.ops import kernels as K
+    from hcache_deepspeed_b200.ops.fp8 import Fp8Weight
+    torch.manual_seed(seed)
+    a = torch.randn(M, Kd, device="cuda").bfloat16()
+    w = (torch.randn(N, Kd, device="cuda") * Kd ** -0.5).bfloat16()
+    bias = torch.randn(N, device="cuda").bfloat16()
+    aq, a_s = K.quantize_fp8_rows(a)
+    w6 = Fp8Weight.from_tensor(w, "e3m2")
+    want = (aq.view(torch.float8_e4m3fn).float() * a_s[:, None]) @ w6.dequantize().t() + bias.float()
+    return K, aq, a_s, w6, bias, want
+
+
+@pytest.mark.parametrize("M", [1, 8, 40, 64])
+@pytest.mark.parametrize("mode", ["store", "gated", "accum"])
+def test_gemm_fp6_weights_skinny(M, mode):
+    """E3M2 (FP6) weights, packed 6 bits each in global memory and unpacked by the TMA, on the decode-size kernel: the
+    result equals the fp32 product of the de-quantised operands (oracle: torch)."""
+    N, Kd = (768 if mode == "gated" else 1000), 2176
+    K, aq, a_s, w6, bias, want = _fp6_case(M, N, Kd, seed=M)
+    if mode == "accum":
+        acc = torch.full((M, N), 0.5, device="cuda", dtype=torch.float32)
+        K.gemm_fp8_accum(aq, a_s, w6.q, w6.scale, acc, bias=bias, w_fmt=1)
+        torch.testing.assert_close(acc, want + 0.5, rtol=2e-3, atol=2e-3)
+    else:
+        gated = mode == "gated"
+        out = torch.empty(M, N // 2 if gated else N, dtype=torch.bfloat16, device="cuda")
+        ws = torch.zeros(K.gemm_fp8_skinny_workspace_bytes(M, N), dtype=torch.uint8, device="cuda")
+        K.gemm_fp8(aq, a_s, w6.q, w6.scale, out, bias=bias, act=K.ACT_SILU if gated else K.ACT_IDENTITY, gated=gated,
+                   workspace=ws, w_fmt=1)
+        ref_out = torch.nn.functional.silu(want[:, 0::2]) * want[:, 1::2] if gated else want
+        torch.testing.assert_close(out.float(), ref_out, rtol=2e-2, atol=2e-2)
+
+
+@pytest.mark.parametrize("M,N,Kd,bn", [(100, 1000, 2176, 0), (100, 512, 1024, 256), (300, 4096, 4096, 0), (2048, 1408, 512, 0)])
+def test_gemm_fp6_weights_token_major(M, N, Kd, bn):
+    """The same weight format on the token-major kernels: single-CTA (M <= 128 or explicit tile) and the CTA-pair kernel."""
+    K, aq, a_s, w6, bias, want = _fp6_case(M, N, Kd, seed=3)
+    out = torch.empty(M, N, dtype=torch.bfloat16, device="cuda")
+    K.gemm_fp8(aq, a_s, w6.q, w6.scale, out, bias=bias, bn=bn, w_fmt=1)
+    torch.testing.assert_close(out.float(), want, rtol=2e-2, atol=3e-2)
+
+
+def test_fp6_linear_module_gpu():
+    """quantization_mode='wf6af16' resolves to the fp6 tcgen05 linear; output tracks the unquantised product."""
+    from types import SimpleNamespace
+    from hcache_deepspeed_b200.inference.v2.modules import heuristics
+    from hcache_deepspeed_b200.inference.v2.modules.configs import DSLinearConfig
+    cfg = DSLinearConfig(in_channels=1024, out_channels=768, input_dtype=torch.bfloat16, output_dtype=torch.bfloat16)
+    lin = heuristics.instantiate_linear(cfg, SimpleNamespace(quantization=SimpleNamespace(quantization_mode="wf6af16")))
+    assert lin.name() == "fp6_tcgen05_linear"
+    torch.manual_seed(0)
+    w = (torch.randn(768, 1024, device="cuda") * 0.03).bfloat16()
+    x = torch.randn(20, 1024, device="cuda").bfloat16()
+    y = lin(x, lin.transform_param(w))
+    want = x.float() @ w.float().t()
+    cos = torch.nn.functional.cosine_similarity(y.float().flatten(), want.flatten(), dim=0)
+    assert cos > 0.99, float(cos)

@@ -199,4 +199,39 @@ def test_fp8_engine_mode_cpu():
     b, _ = eng.put([2], [nxt])
     torch.testing.assert_close(a, b, rtol=1e-4, atol=1e-4)
     with pytest.raises(ValueError, match="wf8af8"):
-        build("wf6af16")
+        build("w4a16")
+
+
+def test_fp6_engine_mode_cpu():
+    """quantization_mode='wf6af16': E3M2 weights packed 6 bits each (input dims that are multiples of 128; others stay
+    E4M3), per-channel scales; pack/unpack round-trips; logits track the unquantised engine."""
+    from hcache_deepspeed_b200.models.arch import ArchSpec
+    from hcache_deepspeed_b200.ops.fp8 import Fp8Weight, pack_6bit, quantize_rows_e3m2, unpack_6bit
+    spec = ArchSpec(model_type="llama", n_layers=2, hidden=128, n_heads=4, n_kv_heads=2, head_dim=32, intermediate=256,
+                    vocab=200, max_positions=256)
+
+    def build(mode):
+        cfg = RaggedInferenceEngineConfig(state_manager=dict(max_tracked_sequences=16, max_ragged_batch_size=128,
+                                                             max_ragged_sequence_count=8, max_context=256,
+                                                             memory_config=dict(mode="allocate", size=16 * 1024 * 1024)),
+                                          hcache={"enabled": True}, quantization={"quantization_mode": mode})
+        return build_engine_from_arch(spec, cfg, seed=1, dtype=torch.float32, device=torch.device("cpu"))
+
+    ref_eng, eng = build(None), build("wf6af16")
+    lw, lw_ref = eng.model().w.layers[0], ref_eng.model().w.layers[0]
+    assert isinstance(lw.w_qkv, Fp8Weight) and lw.w_qkv.fmt == "e3m2" and lw.w_down.fmt == "e3m2"
+    assert lw.w_qkv.q.shape == (lw_ref.w_qkv.shape[0], 128 * 3 // 4) and tuple(lw.w_qkv.shape) == tuple(lw_ref.w_qkv.shape)
+    err = (lw.w_qkv.dequantize() - lw_ref.w_qkv.float()).abs().max() / lw_ref.w_qkv.float().abs().max()
+    assert err < 0.07, float(err)        # 2 mantissa bits: at most 1/16 of the value, relative to the row maximum
+    code, _ = quantize_rows_e3m2(torch.randn(5, 256))
+    assert torch.equal(unpack_6bit(pack_6bit(code)), code) and int(code.max()) < 64
+    g = torch.Generator().manual_seed(0)
+    prompt = torch.randint(0, 200, (40, ), generator=g)
+    want, _ = ref_eng.put([1], [prompt])
+    got, lat = eng.put([1], [prompt])
+    cos = torch.nn.functional.cosine_similarity(got.float().flatten(), want.float().flatten(), dim=0)
+    assert cos > 0.97, float(cos)
+    eng.restore_kv([2], [prompt], [lat[0]])
+    a, _ = eng.put([1], [torch.tensor([7])])
+    b, _ = eng.put([2], [torch.tensor([7])])
+    torch.testing.assert_close(a, b, rtol=1e-4, atol=1e-4)
