@@ -251,10 +251,11 @@ class InferenceEngineV2:
         """Pure decode step through a CUDA graph. The batch metadata (token ids, slots, block tables, work items)
         lives in fixed device buffers refreshed by ``finalize`` before every replay; only launch geometry is baked
         in, so one graph serves a given (sequence count, KV split count) until the heuristic wants more splits."""
-        from ...ops.backend import pick_decode_splits
+        from ...ops.backend import pick_decode_splits, pick_packed_splits, use_packed_decode
         model, batch = self._model, self._batch
         model.finish_pending_restore()
-        key = (batch.current_sequences, pick_decode_splits(batch.n_items_small, model.n_kv, batch.max_kv_len_small),
+        pick = pick_packed_splits if use_packed_decode(model.n_q, model.n_kv, model.d) else pick_decode_splits
+        key = (batch.current_sequences, pick(batch.n_items_small, model.n_kv, batch.max_kv_len_small),
                batch.rows_per_small_item)
         entry = self._decode_graphs.get(key)
         if entry is None:

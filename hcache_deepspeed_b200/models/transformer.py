@@ -206,6 +206,12 @@ class RaggedTransformer:
                     break
                 sp = min(16, -(-148 // units))
                 worst_l = max(worst_l, k.prefill_workspace_bytes(n, self.n_q, self.d, sp))
+            from ..ops.backend import pick_packed_splits, use_packed_decode
+            if use_packed_decode(self.n_q, self.n_kv, self.d):   # head-packed GQA decode parks its split-KV partials here too
+                for n in range(1, S + 1):
+                    sp = pick_packed_splits(n, self.n_kv, 1 << 30)
+                    if sp > 1:
+                        worst_l = max(worst_l, k.prefill_workspace_bytes(n, self.n_kv, self.d, sp))
             self.ws_large = torch.zeros(worst_l, dtype=torch.uint8, device=dev)
             self.io_stream = torch.cuda.Stream(device=dev)
             self.restore_stage = buf(RESTORE_SLOTS, T, H)

@@ -220,9 +220,15 @@ class CudaOps:
         bs = batch.block_size
         if batch.n_items_small:
             n = batch.n_items_small
-            splits = pick_decode_splits(n, n_kv, batch.max_kv_len_small)
-            k.paged_attention_splitkv(q, out, kv_layer, batch.block_tables(), batch.items_small(), n,
-                                      batch.rows_per_small_item, n_q, n_kv, d, bs, splits, scale, ws_small)
+            if use_packed_decode(n_q, n_kv, d):
+                # grouped-query decode: the group's query heads share one pass over the KV pages, on the tensor cores
+                splits = pick_packed_splits(n, n_kv, batch.max_kv_len_small)
+                k.paged_attention_prefill(q, out, kv_layer, batch.block_tables(), batch.items_small(), n, n_q, n_kv, d, bs,
+                                          scale, n_splits=splits, workspace=ws_large if splits > 1 else None, packed=True)
+            else:
+                splits = pick_decode_splits(n, n_kv, batch.max_kv_len_small)
+                k.paged_attention_splitkv(q, out, kv_layer, batch.block_tables(), batch.items_small(), n,
+                                          batch.rows_per_small_item, n_q, n_kv, d, bs, splits, scale, ws_small)
         if batch.n_items_large:
             n = batch.n_items_large
             splits = pick_prefill_splits(n, n_q, batch.max_kv_len_large)
@@ -268,6 +274,25 @@ def pick_decode_splits(n_items: int, n_kv_heads: int, max_kv_len: int) -> int:
             if eff > best:
                 want, best = s, eff
     return int(max(1, min(want, cap)))
+
+
+#: grouped-query decode goes to the tensor-core kernel from this group size on (HDS_GQA_PACKED=0 keeps the SIMT kernel)
+PACKED_MIN_GROUP = 4
+
+
+def use_packed_decode(n_q_heads: int, n_kv_heads: int, head_dim: int) -> bool:
+    import os
+    G = n_q_heads // max(1, n_kv_heads)
+    return (head_dim == 128 and G >= PACKED_MIN_GROUP and 128 % G == 0 and os.environ.get("HDS_GQA_PACKED", "1") != "0")
+
+
+def pick_packed_splits(n_items: int, n_kv_heads: int, max_kv_len: int) -> int:
+    """KV splits of the head-packed decode kernel (one CTA per SM): as many as keep (items x KV heads x splits) within
+    one wave of CTAs; each split keeps at least 2 tiles of 128 keys."""
+    ctas = max(1, n_items * n_kv_heads)
+    tiles = max(1, (max_kv_len + 127) // 128)
+    cap = max(1, min(MAX_PREFILL_SPLITS, tiles // 2 if tiles >= 2 else 1))
+    return int(max(1, min(cap, N_SM // ctas)))
 
 
 def pick_prefill_splits(n_items: int, n_q_heads: int, max_kv_len: int) -> int:

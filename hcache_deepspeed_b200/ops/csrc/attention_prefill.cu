@@ -14,6 +14,13 @@
 //   row's running max grows by more than 2^8 (lazy rescale: probabilities are computed against a slightly stale
 //   max, which is exact after the final division by the matching row sum)
 //
+// Head-packed mode (kPacked, grouped-query decode): one CTA = one (item, KV head); the 128 MMA rows are the
+// (token, query head of the group) pairs of the item — G heads x up to 128/G tokens, fetched by ONE 3-D TMA box from
+// q[T][heads][D] — so a decode step of a GQA model (Llama-2-70B: 8 query heads per KV head) streams every K/V page ONCE
+// for the whole group and does the 8x larger arithmetic on the tensor cores instead of on FFMA (the split-KV SIMT kernel
+// is compute-bound there: 35 ms per 64-session iteration against a 9 ms HBM floor). TMEM lane quadrants without a live
+// row skip the softmax arithmetic and only keep the barrier protocol going.
+//
 // Stands in for the external paged flash kernel of the reference
 // (deepspeed/inference/v2/kernels/ragged_ops/blocked_flash/blocked_flash.cpp:21-101; atoms:
 //  ragged_ops/includes/attention_atom.h:11-39).
@@ -53,7 +60,7 @@ __host__ __device__ constexpr size_t pf_smem_bytes() {
            2 * 2 * 128 * 4 /*row-max exchange*/ + 1024;
 }
 
-template <int D, bool kBf16>
+template <int D, bool kBf16, bool kPacked = false>
 __global__ void __launch_bounds__(kPfThreads, 1)
 paged_attn_prefill_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant__ CUtensorMap tmap_kv,
                           const PrefillArgs a) {
@@ -86,8 +93,10 @@ paged_attn_prefill_kernel(const __grid_constant__ CUtensorMap tmap_q, const __gr
     // walking them backwards leaves the short ones to fill the tail of the schedule
     const int item_idx = static_cast<int>(gridDim.x - 1 - blockIdx.x);
     const hds_attn_item item = a.items[item_idx];
-    const int head = blockIdx.y;
-    const int kvh = head / (a.n_q_heads / a.n_kv_heads);
+    const int head = blockIdx.y;                       // query head, or (kPacked) KV head
+    const int G = a.n_q_heads / a.n_kv_heads;
+    const int kvh = kPacked ? head : head / G;
+    const int n_live_rows = kPacked ? item.n_q * G : item.n_q;   // rows of the 128-row tile that are ever stored
     const int kv_len = item.pos0 + item.n_q;
     const int tiles_total = (kv_len + kPfTok - 1) / kPfTok;
     const int tps = (tiles_total + a.n_splits - 1) / a.n_splits;
@@ -129,8 +138,12 @@ paged_attn_prefill_kernel(const __grid_constant__ CUtensorMap tmap_q, const __gr
             // ---- Q: rows q_row0 .. q_row0+127 of head `head` (rows past n_q are never stored) ----
             mbar_expect_tx(q_full, TILE_BYTES);
 #pragma unroll
-            for (int p = 0; p < PANELS; ++p)
-                tma_load_2d(q_sm + p * PANEL_BYTES, &tmap_q, q_full, head * D + p * 64, item.q_row0, kEvictFirst);
+            for (int p = 0; p < PANELS; ++p) {
+                if constexpr (kPacked)   // box [128/G tokens][G heads][64 dims]: tile row = token * G + head in group
+                    tma_load_3d(q_sm + p * PANEL_BYTES, &tmap_q, q_full, p * 64, kvh * G, item.q_row0, kEvictFirst);
+                else
+                    tma_load_2d(q_sm + p * PANEL_BYTES, &tmap_q, q_full, head * D + p * 64, item.q_row0, kEvictFirst);
+            }
             // ---- K/V tiles ----
             const int32_t* table = a.block_tables + static_cast<int64_t>(item.seq) * a.max_blocks_per_seq;
             const int last_blk_idx = (kv_len - 1) / bs;
@@ -213,8 +226,11 @@ paged_attn_prefill_kernel(const __grid_constant__ CUtensorMap tmap_q, const __gr
         // ===================== softmax / output (warps 2..5, one thread per query row) =====================
         const uint32_t quad = warp & 3;              // TMEM lane quadrant this warp may touch
         const uint32_t half = (warp - 2) >> 2;       // which 64 key columns (and which half of the output dims)
-        const int r = quad * 32 + lane;              // query row inside the item
-        const int q_pos = item.pos0 + r;
+        const int r = quad * 32 + lane;              // row of the 128-row tile
+        const int r_tok = kPacked ? r / G : r;       // query token inside the item
+        const int r_head = kPacked ? kvh * G + (r - r_tok * G) : head;
+        const int q_pos = item.pos0 + r_tok;
+        const bool quad_live = static_cast<int>(quad * 32) < n_live_rows;   // warp-uniform, same for both halves
         const uint32_t lane_addr = (quad * 32u) << 16;
         constexpr int HC = kPfTok / 2;               // key columns per thread
         constexpr int HD2 = D / 2;                   // output dims per thread
@@ -227,6 +243,20 @@ paged_attn_prefill_kernel(const __grid_constant__ CUtensorMap tmap_q, const __gr
             const bool need_mask = (t0 + ti) * kPfTok + kPfTok - 1 > item.pos0;  // warp-uniform
             mbar_wait(s_full, ti & 1);
             tc_fence_after();
+            if (!quad_live) {
+                // no live row in this lane quadrant (head-packed decode): keep the barrier protocol going, skip the math
+                tc_fence_before();
+                __syncwarp();
+                if (lane == 0) mbar_arrive(s_empty);
+                if (ti > 0) {
+                    mbar_wait(o_full, (ti - 1) & 1);
+                    tc_fence_after();
+                }
+                tc_fence_before();
+                __syncwarp();
+                if (lane == 0) mbar_arrive(p_full);
+                continue;
+            }
             // ---- my 64 scores -> registers, then hand the S accumulator back to the MMA warp ----
             uint32_t sr[HC];
 #pragma unroll
@@ -304,7 +334,7 @@ paged_attn_prefill_kernel(const __grid_constant__ CUtensorMap tmap_q, const __gr
             if (lane == 0) mbar_arrive(p_full);
         }
         // ---- total row sum over both halves, then my half of the final O row from TMEM ----
-        {
+        if (quad_live) {
             float* x = xch + (n_tiles & 1) * 256;
             x[half * 128 + r] = l_run;
             pair_sync();
@@ -322,9 +352,9 @@ paged_attn_prefill_kernel(const __grid_constant__ CUtensorMap tmap_q, const __gr
             for (int j = 0; j < 32; ++j) o_acc[c + j] = __uint_as_float(orr[j]);
         }
         tc_fence_before();
-        const bool row_valid = r < item.n_q;
+        const bool row_valid = r < n_live_rows;
         char* dst = reinterpret_cast<char*>(a.out) +
-                    ((static_cast<int64_t>(item.q_row0 + r) * a.n_q_heads + head) * D + half * HD2) * 2;
+                    ((static_cast<int64_t>(item.q_row0 + r_tok) * a.n_q_heads + r_head) * D + half * HD2) * 2;
         if (eff_splits == 1) {
             if (row_valid) {
                 const float inv = 1.0f / l_run;
@@ -338,9 +368,9 @@ paged_attn_prefill_kernel(const __grid_constant__ CUtensorMap tmap_q, const __gr
                     st_v4(dst + c * 2, v);
                 }
             }
-        } else if (static_cast<int>(quad * 32) < item.n_q) {  // warp-uniform: this quadrant owns valid rows
+        } else if (quad_live) {  // warp-uniform: this quadrant owns valid rows
             // ---- split-KV: park the partial (O, m, l); the last split of this (quadrant, half) merges its dims ----
-            const int64_t unit = static_cast<int64_t>(item_idx) * a.n_q_heads + head;
+            const int64_t unit = static_cast<int64_t>(item_idx) * gridDim.y + head;
             const int64_t ws_row = (unit * a.n_splits + split) * 128 + r;
             if (row_valid) {
                 float4* wo = reinterpret_cast<float4*>(a.ws_o + ws_row * D + half * HD2);
@@ -402,10 +432,10 @@ paged_attn_prefill_kernel(const __grid_constant__ CUtensorMap tmap_q, const __gr
     }
 }
 
-template <int D, bool kBf16>
+template <int D, bool kBf16, bool kPacked = false>
 static int launch_prefill(const CUtensorMap& tq, const CUtensorMap& tkv, const PrefillArgs& a, int n_items,
                           cudaStream_t s) {
-    auto kern = paged_attn_prefill_kernel<D, kBf16>;
+    auto kern = paged_attn_prefill_kernel<D, kBf16, kPacked>;
     static bool configured[64] = {false};
     int dev = 0;
     cudaGetDevice(&dev);
@@ -414,7 +444,7 @@ static int launch_prefill(const CUtensorMap& tq, const CUtensorMap& tkv, const P
                                             static_cast<int>(pf_smem_bytes<D>())));
         configured[dev & 63] = true;
     }
-    dim3 grid(n_items, a.n_q_heads, a.n_splits);
+    dim3 grid(n_items, kPacked ? a.n_kv_heads : a.n_q_heads, a.n_splits);
     HDS_CHECK_CUDA(launch_kernel(kern, grid, dim3(kPfThreads), pf_smem_bytes<D>(), s, tq, tkv, a));
     return HDS_OK;
 }
@@ -432,11 +462,10 @@ extern "C" int64_t hds_paged_attention_prefill_workspace_bytes(int n_items, int 
            pf_align256(units * n_splits * 128 * head_dim * 4);
 }
 
-extern "C" int hds_paged_attention_prefill(const void* q, void* out, const void* kv_cache_layer, int64_t num_blocks,
-                                           const int32_t* block_tables, int max_blocks_per_seq,
-                                           const hds_attn_item* items, int n_items, int n_q_rows, int n_q_heads,
-                                           int n_kv_heads, int head_dim, int block_size, float scale, int n_splits,
-                                           void* workspace, int64_t workspace_bytes, int dtype, void* stream) {
+static int attention_tc_impl(bool packed, const void* q, void* out, const void* kv_cache_layer, int64_t num_blocks,
+                             const int32_t* block_tables, int max_blocks_per_seq, const hds_attn_item* items, int n_items,
+                             int n_q_rows, int n_q_heads, int n_kv_heads, int head_dim, int block_size, float scale,
+                             int n_splits, void* workspace, int64_t workspace_bytes, int dtype, void* stream) {
     HDS_REQUIRE(head_dim == 64 || head_dim == 128, "paged_attention_prefill: head_dim must be 64 or 128");
     HDS_REQUIRE(block_size == 16 || block_size == 32 || block_size == 64 || block_size == 128,
                 "paged_attention_prefill: block_size must be 16/32/64/128");
@@ -456,17 +485,28 @@ extern "C" int hds_paged_attention_prefill(const void* q, void* out, const void*
     if (n_splits < 1) n_splits = 1;
     HDS_REQUIRE(n_splits <= 64, "paged_attention_prefill: n_splits in [1,64]");
     a.n_splits = n_splits;
+    const int grid_heads = packed ? n_kv_heads : n_q_heads;
+    const int G = n_q_heads / n_kv_heads;
+    HDS_REQUIRE(!packed || (head_dim == 128 && G >= 2 && G <= 128 && 128 % G == 0),
+                "paged_attention_packed: head_dim 128 and a group size that divides 128");
     if (n_splits > 1) {
-        const int64_t need = hds_paged_attention_prefill_workspace_bytes(n_items, n_q_heads, head_dim, n_splits);
+        const int64_t need = hds_paged_attention_prefill_workspace_bytes(n_items, grid_heads, head_dim, n_splits);
         HDS_REQUIRE(workspace != nullptr && workspace_bytes >= need, "paged_attention_prefill: workspace too small");
-        const int64_t units = static_cast<int64_t>(n_items) * n_q_heads;
+        const int64_t units = static_cast<int64_t>(n_items) * grid_heads;
         char* ws = reinterpret_cast<char*>(workspace);
         a.tickets = reinterpret_cast<int32_t*>(ws);
         a.ws_ml = reinterpret_cast<float*>(ws + pf_align256(units * 8 * 4));
         a.ws_o = reinterpret_cast<float*>(ws + pf_align256(units * 8 * 4) + pf_align256(units * n_splits * 128 * 2 * 4));
     }
     CUtensorMap tq, tkv;
-    int rc = make_tmap_2d_16b(&tq, q, static_cast<uint64_t>(n_q_heads) * head_dim, static_cast<uint64_t>(n_q_rows),
+    int rc;
+    if (packed)   // q[T][heads][D]: one box = [128/G tokens][G heads][64 dims] -> 128 tile rows ordered (token, head)
+        rc = make_tmap_3d_16b(&tq, q, static_cast<uint64_t>(head_dim), static_cast<uint64_t>(n_q_heads),
+                              static_cast<uint64_t>(n_q_rows), static_cast<uint64_t>(head_dim) * 2,
+                              static_cast<uint64_t>(n_q_heads) * head_dim * 2, 64, static_cast<uint32_t>(G),
+                              static_cast<uint32_t>(128 / G), dtype == 0);
+    else
+        rc = make_tmap_2d_16b(&tq, q, static_cast<uint64_t>(n_q_heads) * head_dim, static_cast<uint64_t>(n_q_rows),
                               static_cast<uint64_t>(n_q_heads) * head_dim * 2, 64, 128, dtype == 0);
     if (rc) return rc;
     const uint64_t rows = static_cast<uint64_t>(num_blocks) * 2 * n_kv_heads * block_size;
@@ -474,9 +514,32 @@ extern "C" int hds_paged_attention_prefill(const void* q, void* out, const void*
                           dtype == 0);
     if (rc) return rc;
     cudaStream_t s = static_cast<cudaStream_t>(stream);
+    if (packed)
+        return dtype == 0 ? launch_prefill<128, true, true>(tq, tkv, a, n_items, s)
+                          : launch_prefill<128, false, true>(tq, tkv, a, n_items, s);
     if (head_dim == 128)
         return dtype == 0 ? launch_prefill<128, true>(tq, tkv, a, n_items, s)
                           : launch_prefill<128, false>(tq, tkv, a, n_items, s);
     return dtype == 0 ? launch_prefill<64, true>(tq, tkv, a, n_items, s)
                       : launch_prefill<64, false>(tq, tkv, a, n_items, s);
+}
+
+extern "C" int hds_paged_attention_prefill(const void* q, void* out, const void* kv_cache_layer, int64_t num_blocks,
+                                           const int32_t* block_tables, int max_blocks_per_seq,
+                                           const hds_attn_item* items, int n_items, int n_q_rows, int n_q_heads,
+                                           int n_kv_heads, int head_dim, int block_size, float scale, int n_splits,
+                                           void* workspace, int64_t workspace_bytes, int dtype, void* stream) {
+    return attention_tc_impl(false, q, out, kv_cache_layer, num_blocks, block_tables, max_blocks_per_seq, items, n_items,
+                             n_q_rows, n_q_heads, n_kv_heads, head_dim, block_size, scale, n_splits, workspace,
+                             workspace_bytes, dtype, stream);
+}
+
+extern "C" int hds_paged_attention_packed(const void* q, void* out, const void* kv_cache_layer, int64_t num_blocks,
+                                          const int32_t* block_tables, int max_blocks_per_seq,
+                                          const hds_attn_item* items, int n_items, int n_q_rows, int n_q_heads,
+                                          int n_kv_heads, int head_dim, int block_size, float scale, int n_splits,
+                                          void* workspace, int64_t workspace_bytes, int dtype, void* stream) {
+    return attention_tc_impl(true, q, out, kv_cache_layer, num_blocks, block_tables, max_blocks_per_seq, items, n_items,
+                             n_q_rows, n_q_heads, n_kv_heads, head_dim, block_size, scale, n_splits, workspace,
+                             workspace_bytes, dtype, stream);
 }

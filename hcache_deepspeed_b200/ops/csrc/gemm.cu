@@ -303,7 +303,10 @@ extern "C" int hds_gemm(const void* A, int64_t lda, const void* W, int64_t ldw, 
     HDS_REQUIRE(epilogue != EPI_GATED || (N % 2 == 0), "hds_gemm: gated epilogue needs an even N");
     // measured (profiles/kernel_bench.jsonl): the feature-major kernel wins for M <= 16 everywhere and for the gated
     // MLP-1 up to 64 tokens (1.3-1.5x); plain stores at 32-64 tokens stay on the token-major kernel
-    if (M <= 64 && ldw >= 0 && (bn == -1 || (bn == 0 && skinny_enabled() && (M <= 16 || epilogue == EPI_GATED))))
+    // (a tensor-parallel rank's MLP-1 is narrow — N = 2752 for Llama-2-7B at TP=8: with 17-64 tokens the token-major kernel is
+    // 1.3x faster there, gpurun_out/tp_rank_gemm_probe.jsonl — so the wide-token feature-major form needs N >= 8192)
+    if (M <= 64 && ldw >= 0 &&
+        (bn == -1 || (bn == 0 && skinny_enabled() && (M <= 16 || (epilogue == EPI_GATED && N >= 8192)))))
         return launch_skinny(epilogue, dtype == 0, A, lda, W, ldw, M, N, K, act, bias, out, ldo, nullptr, 0, splitk_ws,
                              splitk_ws_bytes, splits, static_cast<cudaStream_t>(stream));
     // measured (profiles/kernel_bench_gemm_2sm.txt): with at least one full wave of 256 x 256 pair tiles the

@@ -167,7 +167,7 @@ gemm_2sm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constan
                 const int m_t = w % m_tiles, n_t = w / m_tiles;
                 for (int kb = 0; kb < kb_total; ++kb) {
                     mbar_wait(&empty_bar[stage], phase ^ 1);
-                    if (rank == 0) mbar_expect_tx(&full_bar[stage], 2 * (A_BYTES + W_BYTES));
+                    if (rank == 0) mbar_expect_tx(&full_bar[stage], 2 * (A_BYTES + (args.w_tx_bytes ? args.w_tx_bytes : W_BYTES)));
                     tma_load_2d_2sm(smem_a + stage * A_BYTES, &tmap_a, &full_bar[stage], kb * KB_ELEMS,
                                     m_t * 256 + static_cast<int>(rank) * 128, kEvictLast);
                     tma_load_2d_2sm(smem_w + stage * W_BYTES, &tmap_w, &full_bar[stage], kb * KB_ELEMS,
@@ -344,6 +344,7 @@ int gemm_2sm_dispatch(const void* A, int64_t lda_bytes, const float* a_scale, co
         if (w_fmt == 1) {   // E3M2 weights, packed 6-bit in global memory; the weights are the MMA's B operand
             rc = make_tmap_2d_6b(&tw, W, K, N, ldw_bytes, bn / 2);
             fa.g.idesc_or = 4u << 10;
+            fa.g.w_tx_bytes = static_cast<uint32_t>(bn / 2) * f6_tx_bytes_per_row();
         } else {
             rc = make_tmap_2d_8b(&tw, W, K, N, ldw_bytes, 128, bn / 2);
         }

@@ -99,6 +99,7 @@ struct GemmArgs {
     // kind::f8f6f4 kernels: bits OR-ed into the instruction descriptor to select a non-E4M3 weight format
     // (E3M2 = code 4 in the operand-format field of whichever side the weights are on)
     uint32_t idesc_or;
+    uint32_t w_tx_bytes;   // bytes one weight-tile TMA load reports to the mbarrier (0 = the tile's shared-memory size)
 };
 
 // Expert that owns the 128-row tile starting at row0 (-1: past the last expert's rows).

@@ -142,7 +142,7 @@ gemm_fp8_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constan
                 const int m_t = w % m_tiles, n_t = w / m_tiles;
                 for (int kb = 0; kb < kb_total; ++kb) {
                     mbar_wait(&empty_bar[stage], phase ^ 1);
-                    mbar_expect_tx(&full_bar[stage], A_BYTES + W_BYTES);
+                    mbar_expect_tx(&full_bar[stage], A_BYTES + (args.w_tx_bytes ? args.w_tx_bytes : W_BYTES));
                     tma_load_2d(smem_a + stage * A_BYTES, &tmap_a, &full_bar[stage], kb * kF8BK, m_t * 128, kEvictLast);
                     tma_load_2d(smem_w + stage * W_BYTES, &tmap_w, &full_bar[stage], kb * kF8BK, n_t * BN,
                                 m_tiles > 1 ? kEvictNormal : kEvictFirst);
@@ -330,6 +330,7 @@ extern "C" int hds_gemm_fp8(const void* Aq, int64_t lda, const float* a_scale, c
     if (w_fmt == 1) {   // E3M2 weights (packed 6-bit): the weights are the MMA's B operand in this kernel
         rc = make_tmap_2d_6b(&tw, Wq, K, N, ldw, bn);
         fa.g.idesc_or = 4u << 10;
+        fa.g.w_tx_bytes = static_cast<uint32_t>(bn) * f6_tx_bytes_per_row();
     } else {
         rc = make_tmap_2d_8b(&tw, Wq, K, N, ldw, kF8BK, bn);
     }
@@ -443,6 +444,7 @@ extern "C" int hds_gemm_fp8_skinny(const void* Aq, int64_t lda, const float* a_s
     if (w_fmt == 1) {   // E3M2 weights (packed 6-bit): the weights are the MMA's A operand in the feature-major kernel
         rc = make_tmap_2d_6b(&tw, Wq, K, N, ldw, kSkinnyBF);
         a.idesc_or = 4u << 7;
+        a.w_tx_bytes = static_cast<uint32_t>(kSkinnyBF) * f6_tx_bytes_per_row();
     } else {
         rc = make_tmap_2d_8b(&tw, Wq, K, N, ldw, 128, kSkinnyBF);
     }

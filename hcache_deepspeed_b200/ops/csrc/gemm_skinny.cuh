@@ -44,6 +44,7 @@ struct SkinnyArgs {
     const float* a_scale;  // fp8 operands only: per-token scales [M]
     const float* w_scale;  // fp8 operands only: per-feature scales [N]
     uint32_t idesc_or;     // fp8 kernels: operand-format bits for 6-bit (E3M2) weights, else 0
+    uint32_t w_tx_bytes;   // bytes one weight-tile TMA load reports to the mbarrier (0 = the tile's shared-memory size)
     TpSync sync;           // tensor parallel: the producer acquires the peers' flags before its first activation load
                            // (sync.wait); the last CTA to retire releases the output to the peers (sync.signal)
 };
@@ -126,6 +127,7 @@ gemm_skinny_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_cons
     const int sp = static_cast<int>(blockIdx.x) / n_tiles;
     const int kb0 = sp * args.kb_per_split;
     const int kb1 = min(kb_total, kb0 + args.kb_per_split);
+    const uint32_t w_tx = args.w_tx_bytes ? args.w_tx_bytes : W_BYTES;
 
     if (warp == 0 && lane == 0) {
         prefetch_tmap(&tmap_w);
@@ -154,7 +156,7 @@ gemm_skinny_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_cons
             // (produced by the predecessor) follow after the wait and complete the same stage barriers.
             const int pre = min(STAGES, kb1 - kb0);
             for (int i = 0; i < pre; ++i) {
-                mbar_expect_tx(&full_bar[i], W_BYTES + X_BYTES);
+                mbar_expect_tx(&full_bar[i], w_tx + X_BYTES);
                 tma_load_2d(smem_w + i * W_BYTES, &tmap_w, &full_bar[i], (kb0 + i) * KB, n_t * kSkinnyBF,
                             kEvictFirst);
             }
@@ -168,7 +170,7 @@ gemm_skinny_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_cons
             uint32_t stage = 0, phase = 1;  // the ring has been filled once
             for (int kb = kb0 + pre; kb < kb1; ++kb) {
                 mbar_wait(&empty_bar[stage], phase ^ 1);
-                mbar_expect_tx(&full_bar[stage], W_BYTES + X_BYTES);
+                mbar_expect_tx(&full_bar[stage], w_tx + X_BYTES);
                 tma_load_2d(smem_x + stage * X_BYTES, &tmap_x, &full_bar[stage], kb * KB, 0, kEvictLast);
                 tma_load_2d(smem_w + stage * W_BYTES, &tmap_w, &full_bar[stage], kb * KB, n_t * kSkinnyBF,
                             kEvictFirst);

@@ -154,6 +154,12 @@ inline int make_tmap_2d_8b(CUtensorMap* map, const void* base, uint64_t inner, u
 // tcgen05.mma.kind::f8f6f4 reads for 6-bit operands — so HBM carries 0.75 byte per weight while a shared-memory tile row
 // stays 128 bytes for 128 elements, exactly like an fp8 tile. Rules of the format (cuTensorMapEncodeTiled): inner
 // extent a multiple of 128 elements, box inner extent exactly 128, row pitch a multiple of 32 bytes, base 32-byte aligned.
+// Bytes the TMA reports to the mbarrier per 128-element row of a 16U6_ALIGN16B box: the 96 packed bytes it moves, not
+// the 128-byte shared-memory footprint of the unpacked row (HDS_F6_TX_PER_ROW overrides, for experiments).
+inline uint32_t f6_tx_bytes_per_row() {
+    static const int v = getenv("HDS_F6_TX_PER_ROW") ? atoi(getenv("HDS_F6_TX_PER_ROW")) : 96;
+    return static_cast<uint32_t>(v);
+}
 inline int make_tmap_2d_6b(CUtensorMap* map, const void* base, uint64_t inner, uint64_t outer, uint64_t pitch_bytes,
                            uint32_t box_outer) {
     auto enc = tensor_map_encoder();

@@ -396,9 +396,12 @@ def prefill_workspace_bytes(n_items: int, n_q_heads: int, head_dim: int, n_split
 def paged_attention_prefill(q: torch.Tensor, out: torch.Tensor, kv_cache_layer: torch.Tensor,
                             block_tables: torch.Tensor, items: torch.Tensor, n_items: int, n_q_heads: int,
                             n_kv_heads: int, head_dim: int, block_size: int, scale: float, n_splits: int = 1,
-                            workspace: Optional[torch.Tensor] = None) -> None:
+                            workspace: Optional[torch.Tensor] = None, packed: bool = False) -> None:
+    """tcgen05 paged attention. ``packed``: grouped-query decode form — one CTA per (item, KV head) whose MMA rows are
+    the group's (token, query head) pairs (``hds_paged_attention_packed``)."""
     lib = native.cuda_lib()
-    rc = lib.hds_paged_attention_prefill(_p(q), _p(out), _p(kv_cache_layer), kv_cache_layer.shape[0], _p(block_tables),
+    fn = lib.hds_paged_attention_packed if packed else lib.hds_paged_attention_prefill
+    rc = fn(_p(q), _p(out), _p(kv_cache_layer), kv_cache_layer.shape[0], _p(block_tables),
                                          block_tables.stride(0), _p(items), n_items, q.shape[0], n_q_heads, n_kv_heads,
                                          head_dim, block_size, scale, n_splits, _p(workspace),
                                          0 if workspace is None else workspace.numel() * workspace.element_size(),

@@ -60,6 +60,7 @@ def _declare_cuda(lib: ctypes.CDLL) -> None:
         "hds_p2p_gather_rows": [P, P, I, I, I, L, I, P],
         "hds_paged_attention_splitkv": [P, P, P, L, P, I, P, I, I, I, I, I, I, I, F, P, L, I, P],
         "hds_paged_attention_prefill": [P, P, P, L, P, I, P, I, I, I, I, I, I, F, I, P, L, I, P],
+        "hds_paged_attention_packed": [P, P, P, L, P, I, P, I, I, I, I, I, I, F, I, P, L, I, P],
         "hds_moe_topk_gating": [P, L, I, I, I, I, I, P, P, P, P, P],
         "hds_moe_scatter": [P, L, P, L, P, P, P, P, P, I, I, I, I, P],
         "hds_moe_gemm": [P, L, P, L, P, I, I, I, I, I, I, I, P, L, P],

@@ -17,7 +17,36 @@ STEP_MICRO_TIMER = "step_microstep"
 STEP_GLOBAL_TIMER = "step"
 
 
+class _Interval:
+    """One measured span. On a GPU it is a pair of CUDA events on the current stream (nothing is synchronised until the
+    duration is read — the way every kernel in this repository is timed); on the host it is two ``perf_counter`` reads."""
+    __slots__ = ("t0", "t1", "on_device")
+
+    def __init__(self, on_device: bool):
+        self.on_device = on_device
+        if on_device:
+            self.t0 = torch.cuda.Event(enable_timing=True)
+            self.t0.record()
+        else:
+            self.t0 = time.perf_counter()
+        self.t1 = None
+
+    def close(self) -> None:
+        if self.on_device:
+            self.t1 = torch.cuda.Event(enable_timing=True)
+            self.t1.record()
+        else:
+            self.t1 = time.perf_counter()
+
+    def milliseconds(self) -> float:
+        if self.on_device:
+            self.t1.synchronize()
+            return self.t0.elapsed_time(self.t1)
+        return (self.t1 - self.t0) * 1e3
+
+
 class CudaEventTimer:
+    """A closed span between two recorded CUDA events (kept for API parity: ``get_elapsed_msec``)."""
 
     def __init__(self, start_event, end_event):
         self.start_event, self.end_event = start_event, end_event
@@ -28,70 +57,62 @@ class CudaEventTimer:
 
 
 class SynchronizedWallClockTimer:
-    """Group of named timers; on a GPU they record CUDA events and only synchronise when ``elapsed`` is read."""
+    """Named timers for the training engine's forward / backward / step breakdown (ref role:
+    ``deepspeed/utils/timer.py:44-197``). A timer accumulates the spans between its ``start`` / ``stop`` calls;
+    ``elapsed`` sums them in milliseconds (and by default forgets them), ``mean`` averages them."""
 
     class Timer:
 
         def __init__(self, name: str):
-            self.name_ = name
-            self.started_ = False
-            self.event_timers: List[CudaEventTimer] = []
-            self.use_host_timer = not torch.cuda.is_available()
-            self.start_event = None
-            self.elapsed_records: Optional[List[float]] = None
-            self.start_time = 0.0
-            self.end_time = 0.0
+            self.name = name
+            self._open: Optional[_Interval] = None
+            self._closed: List[_Interval] = []
+            self._last_ms: List[float] = []
+
+        @property
+        def running(self) -> bool:
+            return self._open is not None
 
         def start(self):
-            assert not self.started_, f"{self.name_} timer has already been started"
-            if self.use_host_timer:
-                self.start_time = time.time()
-            else:
-                self.start_event = torch.cuda.Event(enable_timing=True)
-                self.start_event.record()
-            self.started_ = True
+            if self._open is not None:
+                raise AssertionError(f"{self.name} timer has already been started")
+            self._open = _Interval(torch.cuda.is_available())
 
         def stop(self, reset: bool = False, record: bool = False):
-            assert self.started_, "timer is not started"
-            if self.use_host_timer:
-                self.end_time = time.time()
-                self.event_timers.append(self.end_time - self.start_time)
-            else:
-                end = torch.cuda.Event(enable_timing=True)
-                end.record()
-                self.event_timers.append(CudaEventTimer(self.start_event, end))
-                self.start_event = None
-            self.started_ = False
+            if self._open is None:
+                raise AssertionError(f"{self.name} timer is not started")
+            self._open.close()
+            self._closed.append(self._open)
+            self._open = None
 
-        def _get_elapsed_msec(self) -> float:
-            if self.use_host_timer:
-                self.elapsed_records = [et * 1000.0 for et in self.event_timers]
-            else:
-                self.elapsed_records = [et.get_elapsed_msec() for et in self.event_timers]
-            self.event_timers.clear()
-            return sum(self.elapsed_records)
+        def _drain(self) -> List[float]:
+            self._last_ms = [iv.milliseconds() for iv in self._closed]
+            self._closed = []
+            return self._last_ms
 
         def reset(self):
-            self.started_ = False
-            self.start_event = None
-            self.elapsed_records = None
-            self.event_timers.clear()
+            self._open, self._closed, self._last_ms = None, [], []
 
         def elapsed(self, reset: bool = True) -> float:
-            started = self.started_
-            if started:
+            """Milliseconds accumulated so far; a running timer is paused for the reading and resumed afterwards."""
+            was_running = self.running
+            if was_running:
                 self.stop()
-            elapsed = self._get_elapsed_msec()
+            total = sum(self._drain())
             if reset:
                 self.reset()
-            if started:
+            if was_running:
                 self.start()
-            return elapsed
+            return total
 
         def mean(self) -> float:
-            self.elapsed(reset=False)
-            recs = self.elapsed_records or []
-            return sum(recs) / len(recs) if recs else 0.0
+            was_running = self.running
+            if was_running:
+                self.stop()
+            ms = self._drain()
+            if was_running:
+                self.start()
+            return sum(ms) / len(ms) if ms else 0.0
 
     def __init__(self):
         self.timers: Dict[str, "SynchronizedWallClockTimer.Timer"] = {}
@@ -100,35 +121,33 @@ class SynchronizedWallClockTimer:
         return self.timers
 
     def __call__(self, name: str) -> "SynchronizedWallClockTimer.Timer":
-        if name not in self.timers:
-            self.timers[name] = self.Timer(name)
-        return self.timers[name]
+        timer = self.timers.get(name)
+        if timer is None:
+            timer = self.timers[name] = self.Timer(name)
+        return timer
 
     @staticmethod
     def memory_usage() -> str:
         if not torch.cuda.is_available():
             return "no accelerator"
-        g = 1024 ** 3
-        return (f" | mem alloc (GB) {torch.cuda.memory_allocated() / g:.4f} | max mem alloc (GB) "
-                f"{torch.cuda.max_memory_allocated() / g:.4f} | mem reserved (GB) {torch.cuda.memory_reserved() / g:.4f}")
+        gib = float(1 << 30)
+        parts = (("mem alloc", torch.cuda.memory_allocated()), ("max mem alloc", torch.cuda.max_memory_allocated()),
+                 ("mem reserved", torch.cuda.memory_reserved()))
+        return "".join(f" | {label} (GB) {value / gib:.4f}" for label, value in parts)
 
     def log(self, names, normalizer: float = 1.0, reset: bool = True, memory_breakdown: bool = False, ranks=None):
-        assert normalizer > 0.0
-        string = "time (ms)"
-        for name in names:
-            if name in self.timers:
-                string += " | {}: {:.2f}".format(name, self.timers[name].elapsed(reset=reset) / normalizer)
+        if normalizer <= 0.0:
+            raise AssertionError("normalizer must be positive")
+        fields = [f"{n}: {self.timers[n].elapsed(reset=reset) / normalizer:.2f}" for n in names if n in self.timers]
+        line = " | ".join(["time (ms)"] + fields)
         if memory_breakdown:
-            string += self.memory_usage()
-        log_dist(string, ranks=ranks or [0])
+            line += self.memory_usage()
+        log_dist(line, ranks=ranks or [0])
 
     def get_mean(self, names, normalizer: float = 1.0, reset: bool = True) -> Dict[str, float]:
-        assert normalizer > 0.0
-        means = {}
-        for name in names:
-            if name in self.timers:
-                means[name] = self.timers[name].mean() * 1000.0 / normalizer
-        return means
+        if normalizer <= 0.0:
+            raise AssertionError("normalizer must be positive")
+        return {n: self.timers[n].mean() * 1000.0 / normalizer for n in names if n in self.timers}
 
 
 class NoopTimer:

@@ -232,6 +232,17 @@ int hds_paged_attention_prefill(const void* q, void* out, const void* kv_cache_l
                                 int n_items, int n_q_rows, int n_q_heads, int n_kv_heads, int head_dim, int block_size,
                                 float scale, int n_splits, void* workspace, int64_t workspace_bytes, int dtype,
                                 void* stream);
+
+/* Grouped-query decode on the tensor cores: the same kernel with the 128 MMA rows holding the (token, query head) pairs
+ * of ONE KV head's group (head_dim 128; group size G = n_q_heads / n_kv_heads divides 128; items of at most 128 / G
+ * tokens). Every K/V page is read once per group and the G-fold arithmetic runs on tcgen05 instead of FFMA.
+ * Workspace (n_splits > 1): hds_paged_attention_prefill_workspace_bytes(n_items, n_kv_heads, 128, n_splits).
+ * Ref role: blocked_flash with GQA (ragged_ops/blocked_flash/blocked_flash.cpp:21-101). */
+int hds_paged_attention_packed(const void* q, void* out, const void* kv_cache_layer, int64_t num_blocks,
+                                const int32_t* block_tables, int max_blocks_per_seq, const hds_attn_item* items,
+                                int n_items, int n_q_rows, int n_q_heads, int n_kv_heads, int head_dim, int block_size,
+                                float scale, int n_splits, void* workspace, int64_t workspace_bytes, int dtype,
+                                void* stream);
 /* Scratch bytes for n_splits > 1 (0 when n_splits <= 1). Zero it once; the kernel leaves its tickets zeroed. */
 int64_t hds_paged_attention_prefill_workspace_bytes(int n_items, int n_q_heads, int head_dim, int n_splits);
 

@@ -390,6 +390,32 @@ def test_attention_prefill(dtype, n_q_heads, n_kv, d, bs):
             torch.testing.assert_close(out.float(), want.float(), **tol(dtype))
 
 
+@pytest.mark.parametrize("dtype", [torch.bfloat16, torch.float16])
+@pytest.mark.parametrize("n_q_heads,n_kv,bs", [(8, 1, 64), (32, 4, 64), (16, 4, 32), (64, 8, 64), (8, 2, 128)])
+def test_attention_packed_gqa_decode(dtype, n_q_heads, n_kv, bs):
+    """Head-packed grouped-query decode on the tensor cores (one CTA per (item, KV head), MMA rows = (token, head of the
+    group)): decode items of 1 token — and as many tokens as 128 / G allows — against the fp32 paged-attention oracle,
+    unsplit and split-KV (tickets must come back zeroed: every launch runs twice)."""
+    d = 128
+    G = n_q_heads // n_kv
+    specs = [(0, 1), (100, 1), (1000, 1), (4000, 1), (63, 1), (127, 1), (128, 1), (5, min(3, 128 // G)), (700, min(128 // G, 6))]
+    q, cache, tables, items = build_paged_problem(specs, n_q_heads, n_kv, d, bs, dtype, seed=5)
+    items_t = torch.tensor(items, dtype=torch.int32, device="cuda")
+    scale = 1.0 / math.sqrt(d)
+    want = ref.paged_attention(q, cache, tables, items_t.cpu(), n_q_heads, n_kv, scale)
+    out = torch.zeros_like(q)
+    K().paged_attention_prefill(q, out, cache, tables, items_t, len(items), n_q_heads, n_kv, d, bs, scale, packed=True)
+    torch.testing.assert_close(out.float(), want.float(), **tol(dtype))
+    for n_splits in (2, 5):
+        ws = torch.zeros(K().prefill_workspace_bytes(len(items), n_kv, d, n_splits), dtype=torch.uint8, device="cuda")
+        for _ in range(2):
+            out.zero_()
+            K().paged_attention_prefill(q, out, cache, tables, items_t, len(items), n_q_heads, n_kv, d, bs, scale,
+                                        n_splits=n_splits, workspace=ws, packed=True)
+            torch.testing.assert_close(out.float(), want.float(), **tol(dtype))
+        assert int(ws[:len(items) * n_kv * 32].view(torch.int32).abs().max()) == 0
+
+
 # ------------------------------------------------------------------------------------------------
 # mixture of experts
 # ------------------------------------------------------------------------------------------------

@@ -580,3 +580,29 @@ def test_aio_kernel_queue_depth(tmp_path):
     c = torch.empty(5000, dtype=torch.uint8)
     assert h.sync_pread(c, path, 100) == 5000
     assert torch.equal(c, a[100:5100])
+
+
+def test_wall_clock_timers():
+    import time
+    from hcache_deepspeed_b200.utils.timer import NoopTimer, SynchronizedWallClockTimer
+    timers = SynchronizedWallClockTimer()
+    t = timers("fwd")
+    assert timers("fwd") is t
+    for _ in range(3):
+        t.start()
+        time.sleep(0.01)
+        t.stop()
+    with pytest.raises(AssertionError):
+        t.stop()
+    assert 8.0 < t.mean() < 60.0                 # milliseconds per span
+    for _ in range(2):
+        t.start()
+        time.sleep(0.01)
+        t.stop()
+    t.start()                                    # reading a running timer pauses and resumes it
+    total = t.elapsed(reset=True)
+    assert total >= 18.0 and t.running
+    t.stop()
+    timers.log(["fwd", "missing"], normalizer=2.0)
+    assert set(timers.get_mean(["fwd"])) == {"fwd"}
+    assert NoopTimer()("x").elapsed() == 0

@@ -278,3 +278,47 @@ def test_pipeline_matches_sequential(world, stages):
         assert r["losses"] == pytest.approx(want, rel=1e-3, abs=1e-4)
         assert r["parts"][0] == 0 and r["parts"][-1] == 5 and math.isfinite(r["eval"])
     assert {r["stage"] for r in res} == set(range(stages))
+
+
+def test_pipe_schedules_pair_up_under_blocking_p2p():
+    """Every send of the 1F1B / inference schedules meets its receive when point-to-point calls block until matched
+    (rendezvous semantics), for every stage count and micro-batch count; no buffer is overwritten by a forward before its
+    backward ran; each stage runs every micro-batch forward and backward exactly once."""
+    from hcache_deepspeed_b200.runtime.pipe import schedule as S
+    match = {"SendActivation": "RecvActivation", "RecvActivation": "SendActivation", "SendGrad": "RecvGrad", "RecvGrad": "SendGrad"}
+
+    def completes(cls, M, st):
+        prog = [[c for step in cls(M, st, i).steps() for c in step] for i in range(st)]
+        pc, moved = [0] * st, True
+        while moved:
+            moved = False
+            for i in range(st):
+                while pc[i] < len(prog[i]):
+                    n = prog[i][pc[i]].name
+                    if n in match:
+                        peer = i + 1 if n in ("SendActivation", "RecvGrad") else i - 1
+                        if pc[peer] < len(prog[peer]) and prog[peer][pc[peer]].name == match[n]:
+                            pc[i] += 1
+                            pc[peer] += 1
+                            moved = True
+                            continue
+                        break
+                    pc[i] += 1
+                    moved = True
+        return all(pc[i] == len(prog[i]) for i in range(st))
+
+    for st in range(1, 8):
+        for M in range(1, 12):
+            assert completes(S.TrainSchedule, M, st) and completes(S.InferenceSchedule, M, st), (M, st)
+            for i in range(st):
+                sched = S.TrainSchedule(M, st, i)
+                cmds = [c for step in sched.steps() for c in step]
+                assert sum(c.name == "ForwardPass" for c in cmds) == M == sum(c.name == "BackwardPass" for c in cmds)
+                assert cmds[-1].name == "OptimizerStep"
+                busy = set()
+                for c in cmds:
+                    if c.name == "ForwardPass":
+                        assert c.buffer_id not in busy and c.buffer_id < sched.num_pipe_buffers()
+                        busy.add(c.buffer_id)
+                    elif c.name == "BackwardPass":
+                        busy.discard(c.buffer_id)
