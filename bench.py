@@ -49,6 +49,9 @@ def parse():
     p.add_argument("--quant", default="none", choices=["none", "wf8af8"],
                    help="none (default, the bf16 headline configuration) or wf8af8: E4M3 weights + per-token fp8 activations; "
                         "reported with dtype fp8-w8a8 and NOT comparable with the bf16 baseline")
+    p.add_argument("--force-kv-layers", type=int, default=0,
+                   help="restore the LAST N layers from offloaded KV pages and the rest from hidden states (a fixed layer split, "
+                        "e.g. the OPT-30B TP=4 NVMe configuration), instead of what the planner would choose")
     p.add_argument("--plan", default="hidden", choices=["auto", "hidden", "planner", "adaptive"],
                    help="hidden: every layer from hidden states (fastest measured on 1xB200: 20.4 ms vs 21.6 ms); auto: planner mix with a recomputed prefix")
     return p.parse_args()
@@ -172,6 +175,10 @@ def run_ours(a):
     plan = plan_restore(spec, ctx, link, allow_kv=a.plan == "planner", allow_recompute=allow_recompute,
                         extra_compute_s=prefill_s)
     hidden_layers, recompute_layers, kv_layers = plan.layers_of("hidden"), plan.layers_of("none"), plan.layers_of("kv")
+    if a.force_kv_layers > 0:
+        n_kv_forced = min(a.force_kv_layers, spec.n_layers)
+        hidden_layers, recompute_layers = list(range(spec.n_layers - n_kv_forced)), []
+        kv_layers = list(range(spec.n_layers - n_kv_forced, spec.n_layers))
     lat_hidden = latents[hidden_layers[0]:hidden_layers[-1] + 1] if hidden_layers else None  # a contiguous run of layers
     kv_pages = None
     if kv_layers:
@@ -184,7 +191,7 @@ def run_ours(a):
             kv_pages[j].copy_((torch.randn(kv_pages.shape[1:], generator=g) * 0.3).to(torch.bfloat16))
     interleave = plan.interleave
     nvme = None
-    if a.source == "nvme" and tp == 1 and lat_hidden is not None:
+    if a.source == "nvme" and lat_hidden is not None:
         # NVMe tier: the session's hidden states sit in a file; every restore reads them back (one request per layer, all
         # aio threads in flight, O_DIRECT so the page cache cannot serve them) into the pinned staging tensor first
         from hcache_deepspeed_b200.io.aio import AsyncIOHandle
@@ -209,21 +216,19 @@ def run_ours(a):
         for i, uid in enumerate(uids):
             t0, e0, e1 = time.perf_counter(), ev(), ev()
             e0.record()
+            layer_ready = None
             if nvme is not None:
+                # every layer's read is queued now (O_DIRECT, kernel AIO: the page cache cannot serve it); the restore waits
+                # for layer l only when it is about to copy layer l to the device, so disk, PCIe and the projections overlap
                 reqs = [nvme["h"].async_pread(lat_hidden[l], nvme["path"], l * nvme["layer_bytes"])
                         for l in range(lat_hidden.shape[0])]
-                for r_ in reqs:
-                    nvme["h"].wait(r_)
+                layer_ready = lambda l, reqs=reqs: nvme["h"].wait(reqs[l])  # noqa: E731
             if sharded and not kv_layers and not recompute_layers:
-                eng.restore_kv([uid], [ctx_tokens], [lat_slice], do_checks=False, sharded=True)
-            elif sharded:
-                eng.restore_session(uid, ctx_tokens, hidden=lat_hidden, hidden_layers=hidden_layers, kv=kv_pages,
-                                    kv_layers=kv_layers, kv_layer_major=True, recompute_layers=recompute_layers,
-                                    interleave=interleave, sharded=True)
+                eng.restore_kv([uid], [ctx_tokens], [lat_hidden], do_checks=False, sharded=True, layer_ready=layer_ready)
             else:
                 eng.restore_session(uid, ctx_tokens, hidden=lat_hidden, hidden_layers=hidden_layers, kv=kv_pages,
                                     kv_layers=kv_layers, kv_layer_major=True, recompute_layers=recompute_layers,
-                                    interleave=interleave)
+                                    interleave=interleave, sharded=sharded, layer_ready=layer_ready)
             logits, _ = eng.put([uid], [new_tokens[i]], do_checks=False)
             tok = kernels.argmax(logits)
             tok_host = tok.cpu()  # D2H of the first token: the TTFT point

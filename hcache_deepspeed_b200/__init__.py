@@ -6,8 +6,12 @@ from __future__ import annotations
 import json
 from typing import Optional, Union
 
-from . import comm  # noqa: F401
-from .comm.comm import init_distributed  # noqa: F401
+from . import _import_paths
+
+_import_paths.register()   # reference module paths that have no separate implementation here (one table, no shim files)
+
+from . import comm  # noqa: F401,E402
+from .comm.comm import init_distributed  # noqa: F401,E402
 from .utils.logging import log_dist, logger  # noqa: F401
 from .version import __version__  # noqa: F401
 

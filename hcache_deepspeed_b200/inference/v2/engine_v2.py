@@ -114,7 +114,7 @@ class InferenceEngineV2:
     def restore_kv(self, batch_uids: Iterable[int], batch_tokens: Iterable[torch.Tensor],
                    batch_latents: Iterable[Optional[Union[torch.Tensor, LatentHandle]]],
                    layers: Optional[Sequence[int]] = None, do_checks: bool = True,
-                   defer: Optional[bool] = None, sharded: bool = False) -> None:
+                   defer: Optional[bool] = None, sharded: bool = False, layer_ready=None) -> None:
         """Rebuild the KV cache of ``batch_uids`` from saved hidden states instead of recomputing the prompt.
 
         ``batch_tokens`` only supply the token counts (ref: engine_v2.py:108-128); ``batch_latents[i]`` is the host
@@ -128,6 +128,10 @@ class InferenceEngineV2:
         ``sharded`` (tensor parallel, one sequence per call): every rank passes only ITS row slice of the hidden
         states (``latent_row_range``), moves 1/tp of the bytes over its own PCIe link, and the projection kernels
         gather the slices from peer memory over NVLink — restore bandwidth scales with the number of GPUs.
+
+        ``layer_ready(i)``: host callback that blocks until saved layer ``i`` has arrived in the (pinned) latent tensors;
+        called right before that layer's host-to-device copy is queued, so storage reads issued up front overlap the
+        copies and projections of the layers before them (NVMe tier).
         """
         uids, toks, lats = list(batch_uids), list(batch_tokens), list(batch_latents)
         todo = [(u, t, (l.wait() if isinstance(l, LatentHandle) else l)) for u, t, l in zip(uids, toks, lats)
@@ -152,7 +156,8 @@ class InferenceEngineV2:
         self._batch.finalize()
         if defer is None:
             defer = self._config.hcache.overlap_restore
-        self._model.restore_kv(self._batch, [l for _, _, l in todo], layers=layers, defer=bool(defer), sharded=sharded)
+        self._model.restore_kv(self._batch, [l for _, _, l in todo], layers=layers, defer=bool(defer), sharded=sharded,
+                               layer_ready=layer_ready)
         for uid, _, _ in todo:
             self._state_manager.get_sequence(uid).post_forward()
 
@@ -160,7 +165,7 @@ class InferenceEngineV2:
                         hidden_layers: Sequence[int] = (), kv: Optional[torch.Tensor] = None,
                         kv_layers: Sequence[int] = (), recompute_layers: Sequence[int] = (),
                         defer: Optional[bool] = None, interleave: float = 2.5, kv_layer_major: bool = False,
-                        sharded: bool = False) -> None:
+                        sharded: bool = False, layer_ready=None) -> None:
         """Bring one session's context back following a mixed plan (``hcache/planner.py``):
 
         * ``recompute_layers`` — must be the prefix ``0..r-1``: recomputed from ``tokens`` (uses the GPU while the
@@ -196,7 +201,8 @@ class InferenceEngineV2:
         n_hidden = len(list(hidden_layers))
         # start the host-to-device stream of the hidden states FIRST: it then runs under the recomputed prefix
         if n_hidden:
-            model.restore_kv(self._batch, [hidden], layers=list(hidden_layers), defer=True, sharded=sharded)
+            model.restore_kv(self._batch, [hidden], layers=list(hidden_layers), defer=True, sharded=sharded,
+                             layer_ready=layer_ready)
         if len(list(kv_layers)):
             model.restore_kv_pages(seq.all_block_ids, kv, list(kv_layers), defer=bool(defer) and kv_layer_major,
                                    layer_major=kv_layer_major)

@@ -153,3 +153,8 @@ MODEL_TYPE_TO_POLICY = {
 }
 
 __all__ = ["InferenceV2Policy", "POLICIES", "MODEL_TYPE_TO_POLICY", "supported_model_types"] + [c.__name__ for c in set(MODEL_TYPE_TO_POLICY.values())]
+
+# the reference's per-family import paths (llama_v2.policy, opt.model, ...) resolve through one table: family_paths.py
+from . import family_paths as _family_paths  # noqa: E402
+
+_family_paths.register(__name__)

@@ -66,15 +66,75 @@ def gds_available() -> bool:
     return _driver_open
 
 
-class GDSHandle:
-    """Synchronous cuFile reads / writes between a file and a device tensor (call from an I/O thread / side stream
-    owner; cuFile itself is synchronous with respect to the calling thread)."""
+def gds_mode() -> str:
+    """'nvidia-fs' when the kernel module that does the peer-to-peer DMA is loaded, 'compat' when cuFile serves the calls
+    through its own pinned bounce buffers (POSIX reads + cudaMemcpy inside the library), 'unavailable' otherwise."""
+    if not gds_available():
+        return "unavailable"
+    return "nvidia-fs" if os.path.exists("/proc/driver/nvidia-fs/stats") else "compat"
 
-    def __init__(self) -> None:
+
+class GDSHandle:
+    """cuFile reads / writes between a file and a device tensor. ``sync_*`` block the caller; ``async_*`` cut the
+    transfer into ``block_size`` pieces executed by ``threads`` worker threads (cuFile is synchronous per calling thread,
+    so parallel calls at different offsets are how the reference keeps a drive busy too:
+    ``csrc/gds/py_lib/deepspeed_gds_op.cpp:72-140``) and return a request id for :meth:`wait`."""
+
+    def __init__(self, block_size: int = 8 << 20, threads: int = 4) -> None:
         if not gds_available():
             raise RuntimeError("GPUDirect Storage is not available on this system (libcufile / nvidia-fs)")
         self._lib = _load()
         self._registered = {}
+        self._block_size, self._threads = max(4096, block_size), max(1, threads)
+        self._pool = None
+        self._requests = {}
+        self._next_id = 1
+
+    # ---- asynchronous API (ref: deepspeed_py_gds_handle.cpp:59-62 async_pread / async_pwrite / wait) -------------------
+    def _submit(self, write: bool, t: torch.Tensor, path: str, file_offset: int, nbytes: Optional[int]) -> int:
+        from concurrent.futures import ThreadPoolExecutor
+        if self._pool is None:
+            self._pool = ThreadPoolExecutor(max_workers=self._threads, thread_name_prefix="hds-gds")
+        n = nbytes if nbytes is not None else t.numel() * t.element_size()
+        fd, handle = self._open(path, write=write)
+        fn = self._lib.cuFileWrite if write else self._lib.cuFileRead
+        base = ctypes.c_void_p(t.data_ptr())
+        dev = t.device
+
+        def piece(off, length):
+            torch.cuda.set_device(dev)
+            got = fn(handle, base, length, file_offset + off, off)
+            if got < 0:
+                raise OSError(f"cuFile{'Write' if write else 'Read'} failed with {got}")
+            return int(got)
+
+        futs = [self._pool.submit(piece, off, min(self._block_size, n - off)) for off in range(0, max(n, 1), self._block_size)]
+        rid = self._next_id
+        self._next_id += 1
+        self._requests[rid] = (futs, fd, handle, t)
+        return rid
+
+    def async_pread(self, device_tensor: torch.Tensor, path: str, file_offset: int = 0, nbytes: Optional[int] = None) -> int:
+        return self._submit(False, device_tensor, path, file_offset, nbytes)
+
+    def async_pwrite(self, device_tensor: torch.Tensor, path: str, file_offset: int = 0, nbytes: Optional[int] = None) -> int:
+        return self._submit(True, device_tensor, path, file_offset, nbytes)
+
+    def wait(self, request_id: int = 0) -> int:
+        """Bytes moved by ``request_id`` (0: by all outstanding requests); raises the first error of a failed piece."""
+        ids = [request_id] if request_id else list(self._requests)
+        total = 0
+        for rid in ids:
+            futs, fd, handle, _ = self._requests.pop(rid)
+            try:
+                total += sum(f.result() for f in futs)
+            finally:
+                self._lib.cuFileHandleDeregister(handle)
+                os.close(fd)
+        return total
+
+    def pending(self) -> int:
+        return sum(1 for futs, *_ in self._requests.values() if not all(f.done() for f in futs))
 
     def pin_device_tensor(self, t: torch.Tensor) -> None:
         """Register a device buffer once so repeated transfers skip per-call registration."""

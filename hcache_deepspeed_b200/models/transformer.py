@@ -574,7 +574,8 @@ class RaggedTransformer:
         return lw.w_qkv[r0:], (lw.b_qkv[r0:] if lw.b_qkv is not None else None)
 
     def restore_kv(self, batch: RaggedBatchWrapper, latents: Sequence[torch.Tensor],
-                   layers: Optional[Sequence[int]] = None, defer: bool = False, sharded: bool = False) -> None:
+                   layers: Optional[Sequence[int]] = None, defer: bool = False, sharded: bool = False,
+                   layer_ready=None) -> None:
         """Rebuild the paged K/V of the batch's tokens from saved hidden states.
 
         ``latents``: one host tensor per sequence of the batch, ``[n_saved_layers, n_tokens_i, hidden]``, whose
@@ -586,6 +587,10 @@ class RaggedTransformer:
         next ``forward`` immediately before its own layer ``l`` — the new turn's prefill fills the gaps in which
         the compute stream would otherwise wait for PCIe (restore is IO-bound on B200), so time-to-first-token
         approaches the pure transfer time.
+
+        ``layer_ready(i)``: optional host callback invoked right before saved layer ``i`` (index into ``layers``) is
+        copied to the device; it blocks until that layer's bytes are in ``latents`` — the hook that pipelines NVMe reads
+        (issued up front, completed layer by layer) against the host-to-device stream and the projections.
         """
         s, ops = self.spec, self.ops
         layers = list(range(s.n_layers)) if layers is None else list(layers)
@@ -603,6 +608,8 @@ class RaggedTransformer:
         bs = kv.kv_block_size
         if self.device.type != "cuda":
             for i, li in enumerate(layers):
+                if layer_ready is not None:
+                    layer_ready(i)
                 lat = torch.cat([l[i] for l in latents], dim=0).to(self.dtype)
                 wk, bk = self.kv_weight(li)
                 ops.restore_kv_proj(lat, wk, bk, kv.get_cache(li), pos, slot, self.inv_freq, self.n_kv, self.d, s.rot_dim, bs)
@@ -615,7 +622,7 @@ class RaggedTransformer:
         self.restore_pos[:T].copy_(pos, non_blocking=True)
         self.restore_slot[:T].copy_(slot, non_blocking=True)
         st = {"T": T, "layers": layers, "latents": list(latents), "issued": 0, "done": 0, "by_layer": {},
-              "sharded": bool(sharded)}
+              "sharded": bool(sharded), "layer_ready": layer_ready}
         for i, li in enumerate(layers):
             st["by_layer"].setdefault(li, []).append(i)
         self._pending_restore = st
@@ -629,6 +636,8 @@ class RaggedTransformer:
         i = st["issued"]
         k = i % RESTORE_SLOTS
         io = self.io_stream
+        if st.get("layer_ready") is not None:
+            st["layer_ready"](i)      # e.g. wait for the NVMe read of this layer (later layers keep reading meanwhile)
         stage = self.restore_stage_sym[k] if st["sharded"] else self.restore_stage[k]
         with torch.cuda.stream(io):
             if i >= RESTORE_SLOTS:

@@ -235,3 +235,27 @@ def test_fp6_engine_mode_cpu():
     a, _ = eng.put([1], [torch.tensor([7])])
     b, _ = eng.put([2], [torch.tensor([7])])
     torch.testing.assert_close(a, b, rtol=1e-4, atol=1e-4)
+
+
+def test_restore_layer_ready_hook_streams_layers_in_order():
+    """``layer_ready(i)`` is called once per saved layer, in order, before that layer is consumed — the hook that lets
+    storage reads complete layer by layer while earlier layers are already being restored."""
+    cfg = RaggedInferenceEngineConfig(state_manager=dict(max_tracked_sequences=8, max_ragged_batch_size=128,
+                                                         max_ragged_sequence_count=4, max_context=256,
+                                                         memory_config=dict(mode="allocate", size=16 * 1024 * 1024)),
+                                      hcache={"enabled": True})
+    eng = build_engine_from_arch("tiny-llama-test", cfg, seed=2, dtype=torch.float32, device=torch.device("cpu"))
+    prompt = torch.randint(0, 100, (33, ))
+    _, lat = eng.put([1], [prompt])
+    staged = torch.zeros_like(lat[0])          # "storage": a layer's bytes appear only when the hook is asked for them
+    seen = []
+
+    def ready(i):
+        seen.append(i)
+        staged[i].copy_(lat[0][i])
+
+    eng.restore_kv([2], [prompt], [staged], layer_ready=ready)
+    assert seen == list(range(lat[0].shape[0]))
+    a, _ = eng.put([1], [torch.tensor([5])])
+    b, _ = eng.put([2], [torch.tensor([5])])
+    torch.testing.assert_close(a, b, rtol=1e-4, atol=1e-4)
