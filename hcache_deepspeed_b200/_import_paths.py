@@ -18,6 +18,22 @@ import types
 PACKAGE = __name__.rsplit(".", 1)[0]
 
 ALIASES = {
+    # one v1 fused-layer class covers what the reference splits into per-family subclasses
+    "model_implementations.transformers.ds_base": [("model_implementations.transformers.ds_transformer", "DeepSpeedTransformerInference", "DeepSpeedTransformerBase")],
+    "model_implementations.transformers.ds_bert": [("model_implementations.transformers.ds_transformer", "DeepSpeedTransformerInference", "DeepSpeedBERTInference")],
+    "model_implementations.transformers.ds_bloom": [("model_implementations.transformers.ds_transformer", "DeepSpeedTransformerInference", "DeepSpeedBloomInference")],
+    "model_implementations.transformers.ds_gpt": [("model_implementations.transformers.ds_transformer", "DeepSpeedTransformerInference", "DeepSpeedGPTInference")],
+    "model_implementations.transformers.ds_llama2": [("model_implementations.transformers.ds_transformer", "DeepSpeedTransformerInference", "DeepSpeedLlama2Inference")],
+    "model_implementations.transformers.ds_megatron_gpt": [("model_implementations.transformers.ds_transformer", "DeepSpeedTransformerInference", "DeepSpeedMegatronGPTInference")],
+    "model_implementations.transformers.ds_opt": [("model_implementations.transformers.ds_transformer", "DeepSpeedTransformerInference", "DeepSpeedOPTInference")],
+    "ops.transformer.inference.ds_attention": [("model_implementations.transformers.ds_transformer", "DeepSpeedSelfAttention", "DeepSpeedSelfAttention"), ("model_implementations.transformers.ds_transformer", "DeepSpeedSelfAttention", "BloomSelfAttention")],
+    # one compressed-collective back end (error-feedback 1-bit all-reduce over torch.distributed) under the reference's names
+    "runtime.comm.nccl": [("runtime.comm.compressed", "CompressedBackend", "NcclBackend")],
+    "runtime.comm.mpi": [("runtime.comm.compressed", "CompressedBackend", "MpiBackend")],
+    "runtime.comm.hccl": [("runtime.comm.compressed", "CompressedBackend", "HcclBackend")],
+    # the NVMe sweep lives in nvme/tune.py
+    "nvme.perf_run_sweep": [("nvme.tune", "get_sweep_config_dict", "get_sweep_config_dict"), ("nvme.tune", "run_sweep", "run_sweep"), ("nvme.tune", "sweep_main", "sweep_main"), ("nvme.tune", "sweep_points", "sweep_points")],
+    "nvme.perf_generate_param": [("nvme.tune", "convert_to_param", "convert_to_param"), ("nvme.tune", "generate_aio_param", "generate_aio_param"), ("nvme.tune", "generate_main", "generate_main")],
     "checkpoint.reshape_3d_utils": [("checkpoint.reshape", "*", "*"), ("checkpoint.reshape", "meg_2d_parallel_map", "meg_2d_parallel_map"), ("checkpoint.reshape", "model_3d_desc", "model_3d_desc"), ("checkpoint.reshape", "ZeROCheckpoint", "ZeROCheckpoint")],
     "checkpoint.reshape_meg_2d": [("checkpoint.reshape", "*", "*"), ("checkpoint.reshape", "meg_2d_parallel_map", "meg_2d_parallel_map"), ("checkpoint.reshape", "model_3d_desc", "model_3d_desc"), ("checkpoint.reshape", "ZeROCheckpoint", "ZeROCheckpoint")],
     "checkpoint.reshape_utils": [("checkpoint.reshape", "*", "*"), ("checkpoint.reshape", "meg_2d_parallel_map", "meg_2d_parallel_map"), ("checkpoint.reshape", "model_3d_desc", "model_3d_desc"), ("checkpoint.reshape", "ZeROCheckpoint", "ZeROCheckpoint")],
