@@ -540,17 +540,15 @@ def test_small_reference_named_modules():
 
 
 def test_nvme_benchmark_scripts(tmp_path, capsys):
-    import hcache_deepspeed_b200.nvme.validate_async_io  # noqa: F401  (asserts the aio engine is usable)
-    from hcache_deepspeed_b200.nvme import parse_nvme_stats, perf_generate_param, perf_run_sweep, perf_sweep_utils  # noqa: F401
-    from hcache_deepspeed_b200.nvme.ds_aio_job import Job, run_job
+    from hcache_deepspeed_b200.nvme import perf_generate_param, perf_run_sweep  # noqa: F401  (paths kept through the alias table)
     from hcache_deepspeed_b200.nvme.test_ds_aio import main
     from hcache_deepspeed_b200.nvme.test_ds_aio_utils import refine_integer_value
+    from hcache_deepspeed_b200.ops.op_builder import AsyncIOBuilder
+    assert AsyncIOBuilder().is_compatible() and AsyncIOBuilder().load() is not None
     gbps = main(["--folder", str(tmp_path), "--io_size", "2M", "--block_size", "256K", "--queue_depth", "4", "--read",
                  "--loops", "1", "--no_direct"])
     assert gbps > 0 and "read:" in capsys.readouterr().out
-    assert refine_integer_value("4K") == 4096 and perf_sweep_utils.READ_OP_DESC == "read"
-    out = tmp_path / "job.log"
-    assert run_job(Job(["python", "-c", "print('hello')"], output_file=str(out))) == 0 and "hello" in out.read_text()
+    assert refine_integer_value("4K") == 4096 and callable(perf_run_sweep.sweep_main)
 
 
 def test_aio_kernel_queue_depth(tmp_path):
