@@ -99,9 +99,15 @@ def get_fp32_state_dict_from_zero_checkpoint(checkpoint_dir: str, tag: Optional[
     if world != len(shards):
         raise ValueError(f"Expected {world} of '*_optim_states.pt' under '{ds_dir}' but found {len(shards)} files. "
                          "Possibly due to an overwrite of an old checkpoint, or a checkpoint didn't get saved by one or more processes.")
-    param_shapes = shards[0][PARAM_SHAPES]
-    sd = _merge_stage3(shards, param_shapes, world) if stage == 3 else _merge_stage12(shards, param_shapes, world)
     model_state = _load(get_model_state_file(ds_dir, stage))
+    # shapes live in the model-states file (the reference's layout: utils/zero_to_fp32.py:100-160 there); older checkpoints
+    # of this code base kept them in the optimizer shard
+    param_shapes = model_state.get(PARAM_SHAPES) or shards[0].get(PARAM_SHAPES)
+    if param_shapes is None:
+        raise KeyError(f"no '{PARAM_SHAPES}' in the model-states or optimizer files under {ds_dir}")
+    if isinstance(param_shapes, dict):
+        param_shapes = [param_shapes]
+    sd = _merge_stage3(shards, param_shapes, world) if stage == 3 else _merge_stage12(shards, param_shapes, world)
     buffers = model_state.get("buffers") if stage == 3 else {k: v for k, v in model_state["module"].items()
                                                             if k in set(model_state.get(BUFFER_NAMES, []))}
     for k, v in (buffers or {}).items():
@@ -110,6 +116,17 @@ def get_fp32_state_dict_from_zero_checkpoint(checkpoint_dir: str, tag: Optional[
         for k, v in model_state["module"].items():  # frozen parameters are not in any optimizer group
             if k not in sd:
                 sd[k] = v.float() if torch.is_floating_point(v) else v
+    if stage == 3 and not exclude_frozen_parameters and model_state.get("frozen_param_shapes"):
+        # every rank's model-states file holds its slice of each frozen parameter
+        states = [model_state] + [_load(f) for f in sorted(glob.glob(os.path.join(ds_dir, "zero_pp_rank_*_model_states.pt")),
+                                                            key=lambda f: int(re.search(r"zero_pp_rank_(\d+)_", f).group(1)))][1:]
+        for name, shape in model_state["frozen_param_shapes"].items():
+            n = math.prod(shape) if len(shape) else 1
+            flat = torch.cat([st["frozen_param_fragments"][name].float().reshape(-1) for st in states])
+            sd[name] = flat[:n].view(shape).clone()
+    for alias, stored in (model_state.get("shared_params") or {}).items():
+        if stored in sd and alias not in sd:
+            sd[alias] = sd[stored]
     return sd
 
 

@@ -786,15 +786,33 @@ class DeepSpeedEngine(torch.nn.Module):
 
     def _save_checkpoint(self, save_dir, tag, client_state, exclude_frozen_parameters=False):
         zero_wrapped = isinstance(self.optimizer, (DeepSpeedZeroOptimizer, DeepSpeedZeroOptimizer_Stage3))
+        frozen_shapes = frozen_fragments = None
         if self.zero_optimization_stage() == 3:
-            module_sd = {}  # parameters live in the optimizer partitions
+            module_sd = {}  # trainable parameters live in the optimizer's fp32 partitions (zero_pp_rank_*_optim_states.pt)
             buffers = {k: v for k, v in self.module.state_dict().items() if k not in dict(self.module.named_parameters())}
+            # frozen parameters (LoRA-style / partial fine-tuning) are in no optimizer group: every rank saves ITS slice of each
+            # one next to the shapes, the layout of the reference's zero_pp_rank_*_model_states.pt (engine.py:3508-3560 there)
+            if not exclude_frozen_parameters:
+                frozen_shapes, frozen_fragments = {}, {}
+                for name, p in self.module.named_parameters():
+                    if not p.requires_grad and hasattr(p, "ds_tensor"):
+                        frozen_shapes[name] = torch.Size(p.ds_shape)
+                        frozen_fragments[name] = p.ds_tensor.detach().cpu().clone()
         else:
             module_sd = self.module_state_dict(exclude_frozen_parameters)
             buffers = None
+        # tied parameters: alias name -> the name under which the tensor is stored
+        seen, shared = {}, {}
+        for name, p in self.module.named_parameters(remove_duplicate=False):
+            key = getattr(p, "ds_id", None) if hasattr(p, "ds_id") else p.data_ptr()
+            if key in seen and seen[key] != name:
+                shared[name] = seen[key]
+            else:
+                seen[key] = name
         state = dict(module=module_sd, buffer_names=list(dict(self.module.named_buffers()).keys()), buffers=buffers,
                      optimizer=self.optimizer.state_dict() if (self.optimizer is not None and not zero_wrapped) else None,
-                     param_shapes=self.optimizer._param_shapes() if isinstance(self.optimizer, DeepSpeedZeroOptimizer) else None,
+                     param_shapes=self.optimizer._param_shapes() if zero_wrapped else None,
+                     frozen_param_shapes=frozen_shapes, frozen_param_fragments=frozen_fragments, shared_params=shared,
                      lr_scheduler=self.lr_scheduler.state_dict() if self.lr_scheduler is not None else None,
                      skipped_steps=self.skipped_steps, global_steps=self.global_steps, global_samples=self.global_samples,
                      dp_world_size=self.dp_world_size, mp_world_size=self.mp_world_size,
@@ -826,11 +844,26 @@ class DeepSpeedEngine(torch.nn.Module):
                 custom_load_fn(src=ckpt["module"], dst=self.module)
             else:
                 self.module.load_state_dict(ckpt["module"], strict=load_module_strict)
-        elif ckpt.get("buffers"):
+        else:
             own = dict(self.module.named_buffers())
-            for k, v in ckpt["buffers"].items():
+            for k, v in (ckpt.get("buffers") or {}).items():
                 if k in own:
                     own[k].data.copy_(v)
+            # frozen parameters: this rank's slice goes back into its partition (and into the live tensor when resident)
+            frags = ckpt.get("frozen_param_fragments") or {}
+            if frags:
+                from .zero.partition_parameters import ZeroParamStatus, all_gather_params
+                params = dict(self.module.named_parameters())
+                for name, frag in frags.items():
+                    p = params.get(name)
+                    if p is None or not hasattr(p, "ds_tensor"):
+                        if load_module_strict:
+                            raise KeyError(f"frozen parameter {name} of the checkpoint is not a ZeRO-3 parameter of this module")
+                        continue
+                    p.ds_tensor.copy_(frag.to(p.ds_tensor.dtype))
+                    if p.ds_status == ZeroParamStatus.AVAILABLE:
+                        p.ds_status = ZeroParamStatus.NOT_AVAILABLE
+                        all_gather_params([p])
         self.loaded_checkpoint_dp_world_size = ckpt.get("dp_world_size")
         self.loaded_checkpoint_mp_world_size = ckpt.get("mp_world_size")
         if not load_module_only:
@@ -851,9 +884,17 @@ class DeepSpeedEngine(torch.nn.Module):
                 self.optimizer.refresh_fp32_params()
             if load_lr_scheduler_states and self.lr_scheduler is not None and ckpt.get("lr_scheduler") is not None:
                 self.lr_scheduler.load_state_dict(ckpt["lr_scheduler"])
+        elif self.zero_optimization_stage() == 3:
+            # module-only load under ZeRO-3: the trainable weights exist only as fp32 partitions in the optimizer shard
+            zpath = self._get_zero_ckpt_name(load_dir, tag)
+            if not os.path.exists(zpath):
+                raise FileNotFoundError(f"load_module_only under ZeRO-3 needs {zpath}: the model-states file holds no trainable weights")
+            zsd = self.checkpoint_engine.load(zpath, map_location="cpu")
+            self.optimizer.load_state_dict(zsd["optimizer_state_dict"], load_optimizer_states=False)
         elif hasattr(self.optimizer, "refresh_fp32_params"):
             self.optimizer.refresh_fp32_params()
-        reserved = {"module", "buffer_names", "buffers", "optimizer", "param_shapes", "lr_scheduler", "skipped_steps",
+        reserved = {"module", "buffer_names", "buffers", "optimizer", "param_shapes", "frozen_param_shapes",
+                    "frozen_param_fragments", "shared_params", "lr_scheduler", "skipped_steps",
                     "global_steps", "global_samples", "dp_world_size", "mp_world_size", "ds_config", "ds_version"}
         client_state = {k: v for k, v in ckpt.items() if k not in reserved}
         return os.path.join(load_dir, str(tag)), client_state

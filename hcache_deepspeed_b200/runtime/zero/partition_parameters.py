@@ -52,6 +52,10 @@ def _convert(param: torch.nn.Parameter, group, remote_device: Optional[str], pin
     ws, rank = _group_info(group)
     if dtype is not None and param.dtype.is_floating_point and param.dtype != dtype:
         param.data = param.data.to(dtype)
+    if ws > 1 and param.data.device.type != "meta":
+        # every rank initialised its own copy (possibly from a different RNG state): rank 0's values are THE values, or the
+        # gathered weight would be a patchwork of differently seeded slices and persistent parameters would differ per rank
+        dist.broadcast(param.data, src=dist.get_global_rank(group, 0) if group is not None else 0, group=group)
     param.ds_id = next(_param_id)
     param.ds_shape = param.data.shape
     param.ds_numel = param.data.numel()

@@ -447,8 +447,11 @@ class DeepSpeedZeroOptimizer_Stage3:
                 "partition_count": self.partition_count, "zero_stage": 3,
                 "optimizer_state_dict": self.optimizer.state_dict(),
                 "fp32_flat_groups": [m.detach().clone() for m in self.fp32_partitioned_groups_flat],
-                "param_shapes": [{self.param_names.get(p, f"group{gi}_param{i}"): tuple(p.ds_shape)
-                                  for i, p in enumerate(params)} for gi, params in enumerate(self.fp16_groups)]}
+                "param_shapes": self._param_shapes()}
+
+    def _param_shapes(self):
+        return [{self.param_names.get(p, f"group{gi}_param{i}"): torch.Size(p.ds_shape) for i, p in enumerate(params)}
+                for gi, params in enumerate(self.fp16_groups)]
 
     def load_state_dict(self, *args, **kw):
         with self._Resident(self):

@@ -223,16 +223,20 @@ class DeepSpeedZeroOptimizer:
         psize = buf.numel() // ws
         if ws == 1:
             return buf
-        if self.gradient_predivide_factor != 1.0:
-            buf.div_(self.gradient_predivide_factor)
-        post = ws / self.gradient_predivide_factor
+        # average = (sum / pre) / post with pre * post = world size. postscale (default): pre is the configured predivide
+        # factor (1 unless set) and the rest is divided out after the collective; prescale: everything is divided out BEFORE
+        # the collective so a 16-bit sum over many ranks cannot overflow.
+        pre = self.gradient_predivide_factor if self.postscale_gradients else float(ws)
+        post = ws / pre
+        if pre != 1.0:
+            buf.div_(pre)
         if self.reduce_scatter and self.partition_gradients:
             out = torch.empty(psize, dtype=buf.dtype, device=buf.device)
             dist.reduce_scatter_tensor(out, buf, group=self.dp_process_group)
         else:
             dist.all_reduce(buf, group=self.dp_process_group)
             out = buf.narrow(0, self.rank * psize, psize)
-        return out.div_(post) if self.postscale_gradients else out.div_(post)
+        return out.div_(post) if post != 1.0 else out
 
     def _reduce_micro_batch(self):
         for gi, params in enumerate(self.bit16_groups):
@@ -341,7 +345,7 @@ class DeepSpeedZeroOptimizer:
     # checkpointing
     # -------------------------------------------------------------------------------------------------
     def _param_shapes(self):
-        return [{self.param_names.get(p, f"group{gi}_param{i}"): tuple(p.shape) for i, p in enumerate(params)}
+        return [{self.param_names.get(p, f"group{gi}_param{i}"): torch.Size(p.shape) for i, p in enumerate(params)}
                 for gi, params in enumerate(self.bit16_groups)]
 
     def state_dict(self):

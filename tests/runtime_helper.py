@@ -228,3 +228,53 @@ def ckpt_tools_worker(rank, world, stage, save_dir, mode):
     m = engine.optimizer.single_partition_of_fp32_groups[0]
     out["exp_avg_norm"] = float(engine.optimizer.optimizer.state[m]["exp_avg"].norm())
     return out
+
+
+def zero3_frozen_worker(rank, world, ckpt_dir):
+    """ZeRO-3 with a frozen layer and per-rank RNG seeds: zero.Init must take rank 0's initial values; a checkpoint must
+    carry the frozen parameters (they are in no optimizer group) and restore them — full load and module-only load — and
+    zero_to_fp32 must rebuild the complete fp32 state dict from the shards."""
+    import hcache_deepspeed_b200 as ds
+    from hcache_deepspeed_b200.checkpoint.zero_to_fp32 import get_fp32_state_dict_from_zero_checkpoint
+    from hcache_deepspeed_b200.runtime.zero import GatheredParameters
+    ds.init_distributed(dist_backend="gloo")
+    hidden, micro = 32, 4
+    cfg = {"train_micro_batch_size_per_gpu": micro, "optimizer": {"type": "AdamW", "params": {"lr": 1e-2}},
+           "zero_optimization": {"stage": 3, "stage3_param_persistence_threshold": 40}, "steps_per_print": 1000}
+
+    def gathered(engine):
+        sd = {}
+        for n, p in engine.module.named_parameters():
+            with GatheredParameters([p]):
+                sd[n] = p.data.detach().float().clone()
+        return sd
+
+    def build(seed):
+        torch.manual_seed(seed)                  # DIFFERENT initial weights on every rank / engine
+        model = TinyNet(hidden)
+        for p in model.layers[0].parameters():
+            p.requires_grad_(False)
+        return ds.initialize(model=model, config=cfg)[0]
+
+    engine = build(100 + rank)
+    start = gathered(engine)
+    torch.manual_seed(100)                       # what rank 0 drew
+    want0 = {k: v.float() for k, v in TinyNet(hidden).state_dict().items()}
+    init_matches_rank0 = all(torch.equal(start[k], want0[k]) for k in start)
+    for x, y in make_batches(3, micro * world, hidden):
+        loss = engine(x[rank * micro:(rank + 1) * micro], y[rank * micro:(rank + 1) * micro])
+        engine.backward(loss)
+        engine.step()
+    trained = gathered(engine)
+    frozen_unchanged = all(torch.equal(trained[k], start[k]) for k in trained if k.startswith("layers.0."))
+    engine.save_checkpoint(ckpt_dir, tag="z3")
+    out = {"init_matches_rank0": init_matches_rank0, "frozen_unchanged": frozen_unchanged, "trained": trained}
+    e2 = build(500 + rank)
+    e2.load_checkpoint(ckpt_dir, tag="z3")
+    out["full_load"] = gathered(e2)
+    e3 = build(900 + rank)
+    e3.load_checkpoint(ckpt_dir, tag="z3", load_module_only=True)
+    out["module_only_load"] = gathered(e3)
+    if rank == 0:
+        out["fp32_from_shards"] = {k: v.clone() for k, v in get_fp32_state_dict_from_zero_checkpoint(ckpt_dir, tag="z3").items()}
+    return out

@@ -322,3 +322,17 @@ def test_pipe_schedules_pair_up_under_blocking_p2p():
                         busy.add(c.buffer_id)
                     elif c.name == "BackwardPass":
                         busy.discard(c.buffer_id)
+
+
+def test_zero3_frozen_params_checkpoint_and_init_broadcast_2ranks(tmp_path):
+    from tests.runtime_helper import zero3_frozen_worker
+    res = run_distributed(zero3_frozen_worker, 2, str(tmp_path / "ckpt"))
+    for r in res:
+        assert r["init_matches_rank0"], "zero.Init kept rank-local initial values instead of rank 0's"
+        assert r["frozen_unchanged"]
+        for key in ("full_load", "module_only_load"):
+            for k, v in r["trained"].items():
+                torch.testing.assert_close(r[key][k], v, rtol=0, atol=0, msg=f"{key}: {k}")
+    shards = res[0]["fp32_from_shards"]
+    for k, v in res[0]["trained"].items():
+        torch.testing.assert_close(shards[k], v, rtol=1e-6, atol=1e-7)
