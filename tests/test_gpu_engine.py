@@ -278,3 +278,52 @@ def test_gds_cufile_roundtrip(tmp_path):
     torch.cuda.synchronize()
     assert torch.equal(src, dst2)
     print(f"cuFile mode: {gds.gds_mode()}")
+
+
+def _hf_model(kind):
+    torch.manual_seed(0)
+    if kind == "opt":
+        from transformers import OPTConfig, OPTForCausalLM
+        cfg = OPTConfig(vocab_size=2048, hidden_size=512, num_hidden_layers=3, ffn_dim=2048, num_attention_heads=8,
+                        max_position_embeddings=1024, word_embed_proj_dim=512, do_layer_norm_before=True, dropout=0.0)
+        return OPTForCausalLM(cfg).eval()
+    from transformers import LlamaConfig, LlamaForCausalLM
+    cfg = LlamaConfig(vocab_size=2048, hidden_size=512, intermediate_size=1408, num_hidden_layers=3, num_attention_heads=4,
+                      num_key_value_heads=2, max_position_embeddings=1024)
+    return LlamaForCausalLM(cfg).eval()
+
+
+@pytest.mark.parametrize("kind", ["opt", "llama"])
+def test_v1_init_inference_kernel_inject_gpu(kind):
+    """``init_inference(replace_with_kernel_inject=True)`` on the GPU (v1 API): the injected engine runs the sm_100a
+    kernels, its logits track the HuggingFace model's fp32 logits for a prompt and for a continuation over the live KV
+    cache, and a flushed session restored from its saved hidden states continues identically."""
+    import hcache_deepspeed_b200 as ds
+    from hcache_deepspeed_b200.ops import kernels, native
+    hf32 = _hf_model(kind)
+    vocab = hf32.config.vocab_size
+    g = torch.Generator().manual_seed(1)
+    ctx = torch.randint(0, vocab, (1, 200), generator=g)
+    turn = torch.randint(0, vocab, (1, 16), generator=g)
+    with torch.no_grad():
+        want_ctx = hf32(input_ids=ctx).logits
+        want_turn = hf32(input_ids=torch.cat([ctx, turn], dim=1)).logits[:, 200:]
+    import copy
+    model = copy.deepcopy(hf32).to(torch.bfloat16).cuda()
+    before = kernels.launch_count
+    eng = ds.init_inference(model, dtype=torch.bfloat16, replace_with_kernel_inject=True,
+                            hcache={"enabled": True, "max_context": 1024, "max_batch_tokens": 512, "kv_memory_bytes": 128 << 20})
+    out = eng(input_ids=ctx.cuda(), session_ids=[7]).logits.float().cpu()
+    assert native.cuda_lib_loaded() and kernels.launch_count > before, "the injected engine did not run the native kernels"
+    cos = torch.nn.functional.cosine_similarity(out.flatten(), want_ctx.flatten(), dim=0)
+    assert cos > 0.995, float(cos)
+    lat = eng.hidden_states(7)
+    assert tuple(lat.shape) == (hf32.config.num_hidden_layers, 200, hf32.config.hidden_size)
+    live = eng(input_ids=turn.cuda(), session_ids=[7]).logits.float().cpu()
+    cos = torch.nn.functional.cosine_similarity(live.flatten(), want_turn.flatten(), dim=0)
+    assert cos > 0.995, float(cos)
+    # end of turn: drop the KV cache, rebuild it from the saved hidden states instead of recomputing the prompt
+    eng.flush(7)
+    eng.restore_hidden_states(7, ctx, lat)
+    restored = eng(input_ids=turn.cuda(), session_ids=[7]).logits.float().cpu()
+    torch.testing.assert_close(restored, live, rtol=3e-2, atol=3e-2)
