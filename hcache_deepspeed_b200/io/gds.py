@@ -52,18 +52,80 @@ def _load() -> Optional[ctypes.CDLL]:
     return None
 
 
+_probe_result: Optional[str] = None   # None = not probed yet; "" = usable; otherwise the reason it is not
+
+_PROBE = r"""
+import ctypes, os, sys, tempfile
+sys.path.insert(0, {root!r})
+import torch
+from hcache_deepspeed_b200.io import gds
+lib = gds._load()
+if lib is None:
+    print("REASON libcufile not found"); sys.exit(0)
+st = lib.cuFileDriverOpen()
+if st.err != 0:
+    print("REASON cuFileDriverOpen error", st.err); sys.exit(0)
+gds._driver_open = True
+gds._probe_result = ""
+h = gds.GDSHandle(block_size=1 << 20, threads=2)
+x = torch.arange(1 << 18, dtype=torch.int32, device="cuda")
+path = os.path.join({tmp!r}, "hds_gds_probe_%d.bin" % os.getpid())
+try:
+    h.sync_pwrite(x, path)
+    y = torch.zeros_like(x)
+    h.sync_pread(y, path)
+    torch.cuda.synchronize()
+    print("OK" if torch.equal(x, y) else "REASON cuFile round trip returned different bytes")
+finally:
+    if os.path.exists(path):
+        os.remove(path)
+"""
+
+
+def probe_gds(timeout_s: float = 45.0, directory: Optional[str] = None) -> str:
+    """Try libcufile end to end (driver open, one write, one read) in a CHILD process with a time limit and return ""
+    when it works or the reason when it does not. cuFile calls cannot be interrupted from Python: on a machine whose
+    nvidia-fs / file-system set-up is broken ``cuFileDriverOpen`` or the first transfer may block forever (seen on the
+    B200 boxes of this project's pod), and a serving process must find that out without hanging itself."""
+    import subprocess
+    import sys
+    import tempfile
+    root = os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+    code = _PROBE.format(root=root, tmp=directory or tempfile.gettempdir())
+    proc = subprocess.Popen([sys.executable, "-c", code], stdout=subprocess.PIPE, stderr=subprocess.PIPE, text=True,
+                            start_new_session=True)
+    try:
+        stdout, stderr = proc.communicate(timeout=timeout_s)
+    except subprocess.TimeoutExpired:
+        proc.kill()   # no wait(): a child stuck in an uninterruptible driver call would block the reaper as well
+        return f"libcufile did not answer within {timeout_s:.0f} s (driver open or first transfer blocked)"
+    out = (stdout or "").strip().splitlines()
+    if out and out[-1] == "OK":
+        return ""
+    if out and out[-1].startswith("REASON"):
+        return out[-1][7:]
+    return f"probe process failed (rc={proc.returncode}): {(stderr or '').strip()[-200:]}"
+
+
 def gds_available() -> bool:
-    """True when libcufile loads and its driver opens (needs a GPU and, for real DMA, nvidia-fs)."""
-    global _driver_open
-    if not torch.cuda.is_available():
+    """True when libcufile works on this machine: checked ONCE per process by :func:`probe_gds` (a child process with a
+    time limit), only then is the driver opened here. ``HDS_GDS=0`` switches the path off without probing."""
+    global _driver_open, _probe_result
+    if not torch.cuda.is_available() or os.environ.get("HDS_GDS", "1") == "0":
         return False
-    lib = _load()
-    if lib is None:
+    if _probe_result is None:
+        _probe_result = "libcufile not found" if _load() is None else probe_gds()
+    if _probe_result:
         return False
     if not _driver_open:
-        st = lib.cuFileDriverOpen()
+        st = _load().cuFileDriverOpen()
         _driver_open = st.err == 0
     return _driver_open
+
+
+def gds_unavailable_reason() -> str:
+    """Why :func:`gds_available` is False ("" when it is True or has not been asked yet)."""
+    return _probe_result or ""
 
 
 def gds_mode() -> str:
