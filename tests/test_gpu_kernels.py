@@ -416,6 +416,19 @@ def test_attention_packed_gqa_decode(dtype, n_q_heads, n_kv, bs):
         assert int(ws[:len(items) * n_kv * 32].view(torch.int32).abs().max()) == 0
 
 
+def test_attention_prefill_64_key_tiles_subprocess():
+    """The opt-in 64-key-tile / two-CTAs-per-SM shape of the tensor-core attention kernel (HDS_PREFILL_TILE=64, read once per
+    process): the prefill attention tests of this file are re-run in a child process with the variable set."""
+    import os
+    import subprocess
+    import sys
+    env = dict(os.environ, HDS_PREFILL_TILE="64")
+    res = subprocess.run([sys.executable, "-m", "pytest", __file__, "-q", "-m", "gpu", "-k", "test_attention_prefill and not subprocess",
+                          "--timeout", "120", "-p", "no:cacheprovider"], env=env, capture_output=True, text=True, timeout=300)
+    assert res.returncode == 0, res.stdout[-2000:] + res.stderr[-1000:]
+    assert " passed" in res.stdout
+
+
 # ------------------------------------------------------------------------------------------------
 # mixture of experts
 # ------------------------------------------------------------------------------------------------
