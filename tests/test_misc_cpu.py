@@ -604,3 +604,42 @@ def test_wall_clock_timers():
     timers.log(["fwd", "missing"], normalizer=2.0)
     assert set(timers.get_mean(["fwd"])) == {"fwd"}
     assert NoopTimer()("x").elapsed() == 0
+
+
+def test_cli_entry_points_bench_elastic_ssh(tmp_path, capsys):
+    """bin/hds_bench (collective sweep through the comm facade, single rank over gloo), bin/hds_elastic (plan of an elastic
+    config), bin/hds_ssh (host list parsing)."""
+    import importlib.machinery
+    import importlib.util
+    import json
+    import os
+    from hcache_deepspeed_b200.benchmarks.communication import bus_factor, main as bench_main
+    assert bus_factor("all_reduce", 8) == 2 * 7 / 8 and bus_factor("all_gather", 4) == 0.75 and bus_factor("broadcast", 8) == 1.0
+    env = {k: os.environ.get(k) for k in ("RANK", "WORLD_SIZE", "MASTER_ADDR", "MASTER_PORT", "LOCAL_RANK")}
+    try:
+        assert bench_main(["--op", "all_reduce", "--backend", "gloo", "--minsize", "1024", "--maxsize", "4096", "--trials", "2",
+                           "--warmups", "1"]) == 0
+    finally:
+        for k, v in env.items():
+            if v is None:
+                os.environ.pop(k, None)
+    out = capsys.readouterr().out
+    assert "all_reduce" in out and "busbw" in out and out.count("\n") >= 5
+
+    def load(name):
+        path = os.path.join(os.path.dirname(os.path.dirname(__file__)), "bin", name)
+        loader = importlib.machinery.SourceFileLoader(name, path)
+        spec = importlib.util.spec_from_loader(name, loader)
+        mod = importlib.util.module_from_spec(spec)
+        loader.exec_module(mod)
+        return mod
+
+    cfg = tmp_path / "ds.json"
+    cfg.write_text(json.dumps({"elasticity": {"enabled": True, "max_train_batch_size": 2000, "micro_batch_sizes": [2, 4, 6],
+                                              "min_gpus": 1, "max_gpus": 10000, "min_time": 20, "version": 0.1}}))
+    load("hds_elastic").main(["-c", str(cfg), "-w", "8"])
+    out = capsys.readouterr().out
+    assert "valid GPU counts" in out and "micro-batch per GPU" in out
+    hf = tmp_path / "hostfile"
+    hf.write_text("# comment\nnode1 slots=8\nnode2 slots=8\n\n")
+    assert load("hds_ssh").hosts_of(str(hf)) == ["node1", "node2"]
