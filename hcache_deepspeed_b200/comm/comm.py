@@ -305,7 +305,11 @@ def mpi_discovery(distributed_port: int = 29500, verbose: bool = True):
     rank, world = comm.Get_rank(), comm.Get_size()
     master = None
     if rank == 0:
-        master = subprocess.check_output(["hostname", "-I"]).decode().split()[0]
+        try:
+            master = subprocess.check_output(["hostname", "-I"]).decode().split()[0]
+        except (subprocess.CalledProcessError, OSError, IndexError):
+            import socket
+            master = socket.gethostbyname(socket.gethostname())
     master = comm.bcast(master, root=0)
     proc_name = MPI.Get_processor_name()
     all_procs = comm.allgather(proc_name)
@@ -314,6 +318,103 @@ def mpi_discovery(distributed_port: int = 29500, verbose: bool = True):
                        "MASTER_ADDR": master, "MASTER_PORT": str(distributed_port)})
     if verbose:
         logger.info(f"Discovered MPI settings of world_rank={rank}, local_rank={local_rank}, world_size={world}")
+
+
+_RANK_ENV_SOURCES = (
+    # (rank, local rank, world size, local size) as exported by each process manager
+    ("OMPI_COMM_WORLD_RANK", "OMPI_COMM_WORLD_LOCAL_RANK", "OMPI_COMM_WORLD_SIZE", "OMPI_COMM_WORLD_LOCAL_SIZE"),
+    ("PMI_RANK", "MPI_LOCALRANKID", "PMI_SIZE", "MPI_LOCALNRANKS"),                       # MPICH / Intel MPI (hydra)
+    ("PMIX_RANK", "PMIX_LOCAL_RANK", "PMIX_SIZE", "PMIX_LOCAL_SIZE"),
+    ("MV2_COMM_WORLD_RANK", "MV2_COMM_WORLD_LOCAL_RANK", "MV2_COMM_WORLD_SIZE", "MV2_COMM_WORLD_LOCAL_SIZE"),
+    ("SLURM_PROCID", "SLURM_LOCALID", "SLURM_NTASKS", "SLURM_NTASKS_PER_NODE"),
+)
+AML_MASTER_PORT = 54965
+AML_NCCL_SOCKET_IFNAME = "^docker0,lo"
+
+
+def process_manager_env(env=None):
+    """(rank, local_rank, world, local_size) from the first process manager whose variables are complete, or None.
+    No MPI library is needed for this: mpirun / srun export the numbers to every rank."""
+    env = os.environ if env is None else env
+    for rank_k, local_k, world_k, lsize_k in _RANK_ENV_SOURCES:
+        if rank_k in env and world_k in env:
+            rank, world = int(env[rank_k]), int(env[world_k])
+            local = int(env[local_k]) if local_k in env else rank
+            try:
+                local_size = int(str(env.get(lsize_k, world)).split("(")[0])     # SLURM writes "8(x2)"
+            except ValueError:
+                local_size = world
+            return rank, local, world, local_size
+    return None
+
+
+def _export_ranks(found):
+    rank, local, world, _ = found
+    os.environ.update({"RANK": str(rank), "LOCAL_RANK": str(local), "WORLD_SIZE": str(world)})
+
+
+def patch_aml_env_for_torch_nccl_backend(master_port: int = 6105, verbose: bool = True):
+    """AzureML launches ranks with OpenMPI and names the first node in ``AZ_BATCH_MASTER_NODE`` (host:port; several
+    nodes) or ``AZ_BATCHAI_MPI_MASTER_NODE`` (one node). (ref: comm.py:765)"""
+    found = process_manager_env()
+    if found is None:
+        raise RuntimeError("AzureML job without OpenMPI rank variables: cannot derive RANK / WORLD_SIZE")
+    _export_ranks(found)
+    if found[3] < found[2]:      # more than one node
+        os.environ["MASTER_ADDR"] = os.environ["AZ_BATCH_MASTER_NODE"].split(":")[0]
+        os.environ.setdefault("MASTER_PORT", str(master_port))
+    else:
+        os.environ["MASTER_ADDR"] = os.environ.get("AZ_BATCHAI_MPI_MASTER_NODE", "127.0.0.1")
+        os.environ["MASTER_PORT"] = str(AML_MASTER_PORT)
+    os.environ["NCCL_SOCKET_IFNAME"] = AML_NCCL_SOCKET_IFNAME
+    if verbose:
+        logger.info("Discovered AzureML settings of world_rank={RANK}, local_rank={LOCAL_RANK}, world_size={WORLD_SIZE}, "
+                    "master_addr={MASTER_ADDR}, master_port={MASTER_PORT}".format(**os.environ))
+
+
+def patch_aws_sm_env_for_torch_nccl_backend(verbose: bool = True):
+    """SageMaker: ranks come from OpenMPI; the first host of ``SM_TRAINING_ENV`` is the rendezvous address when the
+    job did not export one. (ref: comm.py:797)"""
+    found = process_manager_env()
+    if found is None:
+        raise RuntimeError("SageMaker job without OpenMPI rank variables: cannot derive RANK / WORLD_SIZE")
+    _export_ranks(found)
+    if "MASTER_ADDR" not in os.environ:
+        import json
+        try:
+            hosts = json.loads(os.environ["SM_TRAINING_ENV"]).get("hosts") or []
+        except (ValueError, AttributeError):
+            hosts = []
+        os.environ["MASTER_ADDR"] = sorted(hosts)[0] if hosts else "127.0.0.1"
+    os.environ.setdefault("MASTER_PORT", "29500")
+    if verbose:
+        logger.info("Discovered AWS SageMaker settings of world_rank={RANK}, local_rank={LOCAL_RANK}, "
+                    "world_size={WORLD_SIZE}, master_addr={MASTER_ADDR}, master_port={MASTER_PORT}".format(**os.environ))
+
+
+def env_discovery(distributed_port: int = 29500, verbose: bool = True) -> bool:
+    """Rank variables from mpirun / srun without an MPI library. The rendezvous address must already be known
+    (``MASTER_ADDR``, or a single-node job, or SLURM's node list); returns False when it is not, so that the caller
+    can fall back to ``mpi_discovery`` (which broadcasts it)."""
+    found = process_manager_env()
+    if found is None:
+        return False
+    rank, local, world, local_size = found
+    if "MASTER_ADDR" not in os.environ:
+        if local_size >= world:
+            os.environ["MASTER_ADDR"] = "127.0.0.1"
+        elif "SLURM_JOB_NODELIST" in os.environ or "SLURM_NODELIST" in os.environ:
+            from ..launcher.multinode_runner import first_slurm_host
+            os.environ["MASTER_ADDR"] = first_slurm_host(os.environ.get("SLURM_JOB_NODELIST") or
+                                                         os.environ["SLURM_NODELIST"])
+        else:
+            return False
+    _export_ranks(found)
+    os.environ.setdefault("MASTER_PORT", str(distributed_port))
+    if verbose:
+        logger.info(f"Discovered launcher settings of world_rank={rank}, local_rank={local}, world_size={world}, "
+                    f"master_addr={os.environ['MASTER_ADDR']}")
+    return True
 
 
 def in_aml() -> bool:
@@ -349,11 +450,13 @@ def init_distributed(dist_backend: Optional[str] = None, auto_mpi_discovery: boo
         return
     required = ("RANK", "WORLD_SIZE", "MASTER_ADDR", "MASTER_PORT", "LOCAL_RANK")
     if auto_mpi_discovery and not all(k in os.environ for k in required):
-        if "OMPI_COMM_WORLD_SIZE" in os.environ or "PMI_SIZE" in os.environ:
-            try:
-                mpi_discovery(distributed_port=distributed_port, verbose=verbose)
-            except ImportError:
-                pass
+        if in_aml() and not in_dlts():
+            patch_aml_env_for_torch_nccl_backend(verbose=verbose)
+        elif in_aws_sm():
+            patch_aws_sm_env_for_torch_nccl_backend(verbose=verbose)
+        elif process_manager_env() is not None and not env_discovery(distributed_port, verbose):
+            # several nodes and nobody exported the rendezvous address: rank 0 has to broadcast it through MPI
+            mpi_discovery(distributed_port=distributed_port, verbose=verbose)
     os.environ.setdefault("RANK", str(rank if rank >= 0 else 0))
     os.environ.setdefault("WORLD_SIZE", str(world_size if world_size > 0 else 1))
     os.environ.setdefault("LOCAL_RANK", os.environ["RANK"])

@@ -197,3 +197,36 @@ class MVAPICHRunner(_MPIStyle):
 
 RUNNERS = {"pdsh": PDSHRunner, "openmpi": OpenMPIRunner, "mpich": MPICHRunner, "impi": IMPIRunner, "slurm": SlurmRunner,
            "mvapich": MVAPICHRunner}
+
+
+def expand_slurm_nodelist(nodelist: str):
+    """``node[01-03,07],gpu5`` -> [node01, node02, node03, node07, gpu5] (what ``scontrol show hostnames`` prints, without
+    needing scontrol on the rank's node)."""
+    hosts, depth, start = [], 0, 0
+    parts = []
+    for i, ch in enumerate(nodelist):
+        depth += ch == "["
+        depth -= ch == "]"
+        if ch == "," and depth == 0:
+            parts.append(nodelist[start:i])
+            start = i + 1
+    parts.append(nodelist[start:])
+    for part in filter(None, (p.strip() for p in parts)):
+        lb = part.find("[")
+        if lb < 0:
+            hosts.append(part)
+            continue
+        rb = part.index("]", lb)
+        prefix, suffix = part[:lb], part[rb + 1:]
+        for rng in part[lb + 1:rb].split(","):
+            lo, _, hi = rng.partition("-")
+            if not hi:
+                hosts.append(f"{prefix}{lo}{suffix}")
+                continue
+            width = len(lo)
+            hosts.extend(f"{prefix}{n:0{width}d}{suffix}" for n in range(int(lo), int(hi) + 1))
+    return hosts
+
+
+def first_slurm_host(nodelist: str) -> str:
+    return expand_slurm_nodelist(nodelist)[0]

@@ -643,3 +643,76 @@ def test_cli_entry_points_bench_elastic_ssh(tmp_path, capsys):
     hf = tmp_path / "hostfile"
     hf.write_text("# comment\nnode1 slots=8\nnode2 slots=8\n\n")
     assert load("hds_ssh").hosts_of(str(hf)) == ["node1", "node2"]
+
+
+def test_launcher_environment_discovery(monkeypatch):
+    """Rank variables of mpirun / srun / AzureML / SageMaker are mapped to RANK / LOCAL_RANK / WORLD_SIZE / MASTER_*
+    without an MPI library (ref: deepspeed/comm/comm.py:705-808)."""
+    import json
+    import os
+    from hcache_deepspeed_b200.comm import comm as C
+    from hcache_deepspeed_b200.launcher.multinode_runner import expand_slurm_nodelist
+
+    keys = ["RANK", "LOCAL_RANK", "WORLD_SIZE", "MASTER_ADDR", "MASTER_PORT", "NCCL_SOCKET_IFNAME"]
+    keys += [k for row in C._RANK_ENV_SOURCES for k in row]
+    keys += ["AZUREML_EXPERIMENT_ID", "AZ_BATCH_MASTER_NODE", "AZ_BATCHAI_MPI_MASTER_NODE", "SM_TRAINING_ENV", "DLTS_JOB_ID",
+             "SLURM_JOB_NODELIST", "SLURM_NODELIST"]
+
+    def clean():
+        for k in keys:
+            monkeypatch.delenv(k, raising=False)
+
+    clean()
+    assert C.process_manager_env() is None and not C.env_discovery(verbose=False)
+
+    # OpenMPI, one node: loopback rendezvous
+    for k, v in dict(OMPI_COMM_WORLD_RANK="3", OMPI_COMM_WORLD_LOCAL_RANK="3", OMPI_COMM_WORLD_SIZE="4",
+                     OMPI_COMM_WORLD_LOCAL_SIZE="4").items():
+        monkeypatch.setenv(k, v)
+    assert C.process_manager_env() == (3, 3, 4, 4)
+    assert C.env_discovery(distributed_port=29611, verbose=False)
+    assert [os.environ[k] for k in keys[:5]] == ["3", "3", "4", "127.0.0.1", "29611"]
+
+    # OpenMPI, two nodes, no address known: the caller must fall back to MPI broadcast
+    clean()
+    for k, v in dict(OMPI_COMM_WORLD_RANK="5", OMPI_COMM_WORLD_LOCAL_RANK="1", OMPI_COMM_WORLD_SIZE="8",
+                     OMPI_COMM_WORLD_LOCAL_SIZE="4").items():
+        monkeypatch.setenv(k, v)
+    assert not C.env_discovery(verbose=False) and "RANK" not in os.environ
+
+    # SLURM with a compact node list
+    clean()
+    for k, v in dict(SLURM_PROCID="9", SLURM_LOCALID="1", SLURM_NTASKS="16", SLURM_NTASKS_PER_NODE="8(x2)",
+                     SLURM_JOB_NODELIST="gpu[07-08,11],login1").items():
+        monkeypatch.setenv(k, v)
+    assert expand_slurm_nodelist("gpu[07-08,11],login1,a[1-2]b") == ["gpu07", "gpu08", "gpu11", "login1", "a1b", "a2b"]
+    assert C.env_discovery(verbose=False)
+    assert (os.environ["RANK"], os.environ["LOCAL_RANK"], os.environ["WORLD_SIZE"], os.environ["MASTER_ADDR"]) == \
+        ("9", "1", "16", "gpu07")
+
+    # AzureML, several nodes and one node
+    clean()
+    for k, v in dict(AZUREML_EXPERIMENT_ID="x", OMPI_COMM_WORLD_RANK="4", OMPI_COMM_WORLD_LOCAL_RANK="0",
+                     OMPI_COMM_WORLD_SIZE="8", OMPI_COMM_WORLD_LOCAL_SIZE="4", AZ_BATCH_MASTER_NODE="10.0.0.4:6000").items():
+        monkeypatch.setenv(k, v)
+    assert C.in_aml()
+    C.patch_aml_env_for_torch_nccl_backend(verbose=False)
+    assert (os.environ["RANK"], os.environ["MASTER_ADDR"], os.environ["MASTER_PORT"]) == ("4", "10.0.0.4", "6105")
+    assert os.environ["NCCL_SOCKET_IFNAME"] == C.AML_NCCL_SOCKET_IFNAME
+    clean()
+    for k, v in dict(AZUREML_EXPERIMENT_ID="x", OMPI_COMM_WORLD_RANK="1", OMPI_COMM_WORLD_LOCAL_RANK="1",
+                     OMPI_COMM_WORLD_SIZE="2", OMPI_COMM_WORLD_LOCAL_SIZE="2", AZ_BATCHAI_MPI_MASTER_NODE="10.0.0.9").items():
+        monkeypatch.setenv(k, v)
+    C.patch_aml_env_for_torch_nccl_backend(verbose=False)
+    assert (os.environ["MASTER_ADDR"], os.environ["MASTER_PORT"]) == ("10.0.0.9", str(C.AML_MASTER_PORT))
+
+    # SageMaker
+    clean()
+    for k, v in dict(SM_TRAINING_ENV=json.dumps({"hosts": ["algo-2", "algo-1"]}), OMPI_COMM_WORLD_RANK="2",
+                     OMPI_COMM_WORLD_LOCAL_RANK="0", OMPI_COMM_WORLD_SIZE="4").items():
+        monkeypatch.setenv(k, v)
+    assert C.in_aws_sm()
+    C.patch_aws_sm_env_for_torch_nccl_backend(verbose=False)
+    assert (os.environ["RANK"], os.environ["LOCAL_RANK"], os.environ["WORLD_SIZE"], os.environ["MASTER_ADDR"]) == \
+        ("2", "0", "4", "algo-1")
+    clean()
