@@ -131,8 +131,19 @@ class InferenceEngine(torch.nn.Module):
         log_dist(f"init_inference: loaded {n} checkpoint file(s)", [0])
 
     def _has_v2_policy(self) -> bool:
+        """True when the module's architecture is one the ragged executor runs. Variants a family's spec builder rejects
+        (ALiBi Falcon, GPT-2 with per-layer attention scaling, ...) stay on the per-block container path."""
+        from ..models.arch import arch_from_hf_config
         from .v2.model_implementations import MODEL_TYPE_TO_POLICY
-        return getattr(getattr(self.module, "config", None), "model_type", None) in MODEL_TYPE_TO_POLICY
+        cfg = getattr(self.module, "config", None)
+        if getattr(cfg, "model_type", None) not in MODEL_TYPE_TO_POLICY:
+            return False
+        try:
+            arch_from_hf_config(cfg)
+        except (ValueError, TypeError) as e:
+            log_dist(f"init_inference: {cfg.model_type} variant is outside the ragged executor ({e}); using block injection", [0])
+            return False
+        return True
 
     def _apply_v1_injection(self, config) -> None:
         """``replace_with_kernel_inject`` for a family without a ragged-executor policy: swap every block for the fused

@@ -146,7 +146,21 @@ class Qwen2MoePolicy(InferenceV2Policy):
     pass
 
 
+class GPT2Policy(InferenceV2Policy):
+    """GPT-2, GPT-J and GPT-NeoX have no v2 policy in the reference (v1 kernel injection only:
+    ``module_inject/containers/{gpt2,gptj,gptneox}.py``); here they are ordinary families of the one executor."""
+
+
+class GPTJPolicy(InferenceV2Policy):
+    pass
+
+
+class GPTNeoXPolicy(InferenceV2Policy):
+    pass
+
+
 MODEL_TYPE_TO_POLICY = {
+    "gpt2": GPT2Policy, "gptj": GPTJPolicy, "gpt_neox": GPTNeoXPolicy,
     "llama": Llama2Policy, "opt": OPTPolicy, "mistral": MistralPolicy, "mixtral": MixtralPolicy, "falcon": FalconPolicy,
     "phi": PhiPolicy, "phi3": Phi3Policy, "qwen": QwenPolicy, "qwen2": Qwen2Policy, "qwen2_moe": Qwen2MoePolicy,
     "internlm": Llama2Policy,

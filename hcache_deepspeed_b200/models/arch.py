@@ -227,6 +227,62 @@ def _qwen(cfg) -> ArchSpec:
         max_positions=_get(cfg, "seq_length", "max_position_embeddings", default=8192), qkv_bias=True)
 
 
+# ---- families the reference serves only through v1 kernel injection (module_inject/containers/{gpt2,gptj,gptneox}.py).
+# Here they are three more specs for the same executor, so init_inference(replace_with_kernel_inject=True) runs them
+# on the sm_100a kernels with paged KV, and HCache restore works for them too.
+@register_arch("gpt2")
+def _gpt2(cfg) -> ArchSpec:
+    h = _get(cfg, "n_embd", "hidden_size")
+    nh = _get(cfg, "n_head", "num_attention_heads")
+    if _get(cfg, "scale_attn_by_inverse_layer_idx", default=False) or not _get(cfg, "scale_attn_weights", default=True):
+        raise ValueError("GPT-2 variants with non-standard attention scaling are not supported")
+    return ArchSpec(
+        model_type="gpt2", n_layers=_get(cfg, "n_layer", "num_hidden_layers"), hidden=h, n_heads=nh, n_kv_heads=nh,
+        head_dim=h // nh, intermediate=_get(cfg, "n_inner", default=4 * h), vocab=_get(cfg, "vocab_size"), norm="layer",
+        norm_eps=_get(cfg, "layer_norm_epsilon", default=1e-5), act=_get(cfg, "activation_function", default="gelu_new"),
+        gated_mlp=False, pos_emb="learned", learned_pos_offset=0, max_positions=_get(cfg, "n_positions", default=1024),
+        qkv_bias=True, attn_out_bias=True, mlp_bias=True, norm_bias=True, tie_word_embeddings=True)
+
+
+@register_arch("gptj")
+def _gptj(cfg) -> ArchSpec:
+    h = _get(cfg, "n_embd", "hidden_size")
+    nh = _get(cfg, "n_head", "num_attention_heads")
+    hd = h // nh
+    return ArchSpec(
+        model_type="gptj", n_layers=_get(cfg, "n_layer", "num_hidden_layers"), hidden=h, n_heads=nh, n_kv_heads=nh,
+        head_dim=hd, intermediate=_get(cfg, "n_inner", default=4 * h), vocab=_get(cfg, "vocab_size"), norm="layer",
+        norm_eps=_get(cfg, "layer_norm_epsilon", default=1e-5), act=_get(cfg, "activation_function", default="gelu_new"),
+        gated_mlp=False, pos_emb="rope", rope_theta=10000.0, rotary_dim=_get(cfg, "rotary_dim", default=hd),
+        max_positions=_get(cfg, "n_positions", default=2048), qkv_bias=False, attn_out_bias=False, mlp_bias=True,
+        lm_head_bias=True, norm_bias=True, parallel_residual=True,
+        tie_word_embeddings=bool(_get(cfg, "tie_word_embeddings", default=False)),
+        extras={"rope_interleaved_checkpoint": True})     # rows are re-ordered once at load (families.map_gptj)
+
+
+@register_arch("gpt_neox")
+def _gpt_neox(cfg) -> ArchSpec:
+    h = _get(cfg, "hidden_size")
+    nh = _get(cfg, "num_attention_heads")
+    hd = h // nh
+    pct = _get(cfg, "rotary_pct", "partial_rotary_factor")
+    if pct is None:
+        rp = _get(cfg, "rope_parameters", "rope_scaling")
+        pct = rp.get("partial_rotary_factor") if isinstance(rp, dict) else None
+    pct = 0.25 if pct is None else float(pct)
+    theta = _get(cfg, "rotary_emb_base")
+    par = bool(_get(cfg, "use_parallel_residual", default=True))
+    return ArchSpec(
+        model_type="gpt_neox", n_layers=_get(cfg, "num_hidden_layers"), hidden=h, n_heads=nh, n_kv_heads=nh, head_dim=hd,
+        intermediate=_get(cfg, "intermediate_size", default=4 * h), vocab=_get(cfg, "vocab_size"), norm="layer",
+        norm_eps=_get(cfg, "layer_norm_eps", default=1e-5), act=_get(cfg, "hidden_act", default="gelu"), gated_mlp=False,
+        pos_emb="rope", rope_theta=float(theta) if theta is not None else _rope_theta(cfg), rotary_dim=int(hd * pct),
+        max_positions=_get(cfg, "max_position_embeddings", default=2048),
+        qkv_bias=bool(_get(cfg, "attention_bias", default=True)), attn_out_bias=bool(_get(cfg, "attention_bias", default=True)),
+        mlp_bias=True, norm_bias=True, parallel_residual=par, parallel_two_norms=par,
+        tie_word_embeddings=bool(_get(cfg, "tie_word_embeddings", default=False)))
+
+
 @register_arch("mixtral")
 def _mixtral(cfg) -> ArchSpec:
     base = _llama_like(cfg)

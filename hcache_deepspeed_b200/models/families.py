@@ -258,3 +258,126 @@ def map_qwen(name: str, t: torch.Tensor, spec: ArchSpec) -> List[Piece]:
         if parts[1] in table:
             return [(layer, f"mlp.{table[parts[1]]}", t)]
     return []
+
+
+# ---------------------------------------------------------------------------------------------------
+# GPT-2 / GPT-J / GPT-NeoX: served by the reference through v1 kernel injection only
+# (module_inject/containers/{gpt2,gptj,gptneox}.py); here they load into the same executor as everything else.
+# ---------------------------------------------------------------------------------------------------
+@register_mapper("gpt2")
+def map_gpt2(name: str, t: torch.Tensor, spec: ArchSpec) -> List[Piece]:
+    layer, rest = _split_layer(name)
+    kind = name.split(".")[-1]
+    if layer is None:
+        if name.endswith("wte.weight"):
+            return [(None, "embed", t)]
+        if name.endswith("wpe.weight"):
+            return [(None, "pos_embed", t)]
+        if "ln_f." in name:
+            return [(None, "final_norm.g" if kind == "weight" else "final_norm.b", t)]
+        return []  # lm_head is tied to wte
+    parts = rest.split(".")
+    if kind not in ("weight", "bias") or len(parts) < 2:
+        return []  # causal-mask buffers (attn.bias / attn.masked_bias)
+    gb = "g" if kind == "weight" else "b"
+    if parts[0] == "ln_1":
+        return [(layer, f"norm1.{gb}", t)]
+    if parts[0] == "ln_2":
+        return [(layer, f"norm2.{gb}", t)]
+    # HF's Conv1D keeps weights [in, out]: transpose to the [out, in] layout every GEMM here takes
+    w = t.t() if (kind == "weight" and t.dim() == 2) else t
+    sfx = _wb(kind)
+    if parts[0] == "attn" and len(parts) == 3:
+        if parts[1] == "c_attn":
+            q, k, v = w.chunk(3, dim=0)
+            return [(layer, f"attn.q{sfx}", q), (layer, f"attn.k{sfx}", k), (layer, f"attn.v{sfx}", v)]
+        if parts[1] == "c_proj":
+            return [(layer, f"attn.o{sfx}", w)]
+    if parts[0] == "mlp" and len(parts) == 3:
+        if parts[1] == "c_fc":
+            return [(layer, f"mlp.up{sfx}", w)]
+        if parts[1] == "c_proj":
+            return [(layer, f"mlp.down{sfx}", w)]
+    return []
+
+
+def _pairs_to_halves(t: torch.Tensor, spec: ArchSpec) -> torch.Tensor:
+    """GPT-J rotates adjacent pairs (2i, 2i+1); the kernels rotate (i, i + rot/2). Re-ordering the first ``rot`` output
+    rows of every Q and K head the same way leaves every q.k dot product unchanged, so the checkpoint is converted once
+    here instead of carrying a second RoPE variant through the kernels."""
+    d, rot = spec.head_dim, spec.rot_dim
+    perm = torch.cat([torch.arange(0, rot, 2), torch.arange(1, rot, 2), torch.arange(rot, d)])
+    heads = t.shape[0] // d
+    return t.reshape((heads, d) + tuple(t.shape[1:]))[:, perm].reshape(t.shape)
+
+
+@register_mapper("gptj")
+def map_gptj(name: str, t: torch.Tensor, spec: ArchSpec) -> List[Piece]:
+    layer, rest = _split_layer(name)
+    kind = name.split(".")[-1]
+    if layer is None:
+        if name.endswith("wte.weight"):
+            return [(None, "embed", t)]
+        if "ln_f." in name:
+            return [(None, "final_norm.g" if kind == "weight" else "final_norm.b", t)]
+        if name == "lm_head.weight":
+            return [] if spec.tie_word_embeddings else [(None, "lm_head", t)]
+        if name == "lm_head.bias":
+            return [(None, "lm_head_b", t)]
+        return []
+    parts = rest.split(".")
+    if kind not in ("weight", "bias"):
+        return []
+    sfx = _wb(kind)
+    if parts[0] == "ln_1":
+        return [(layer, "norm1.g" if kind == "weight" else "norm1.b", t)]
+    if parts[0] == "attn" and len(parts) == 3:
+        if parts[1] in ("q_proj", "k_proj"):
+            return [(layer, f"attn.{parts[1][0]}{sfx}", _pairs_to_halves(t, spec))]
+        if parts[1] == "v_proj":
+            return [(layer, f"attn.v{sfx}", t)]
+        if parts[1] == "out_proj":
+            return [(layer, f"attn.o{sfx}", t)]
+    if parts[0] == "mlp" and len(parts) == 3:
+        if parts[1] == "fc_in":
+            return [(layer, f"mlp.up{sfx}", t)]
+        if parts[1] == "fc_out":
+            return [(layer, f"mlp.down{sfx}", t)]
+    return []
+
+
+@register_mapper("gpt_neox")
+def map_gpt_neox(name: str, t: torch.Tensor, spec: ArchSpec) -> List[Piece]:
+    layer, rest = _split_layer(name)
+    kind = name.split(".")[-1]
+    if layer is None:
+        if name.endswith("embed_in.weight"):
+            return [(None, "embed", t)]
+        if "final_layer_norm." in name:
+            return [(None, "final_norm.g" if kind == "weight" else "final_norm.b", t)]
+        if name == "embed_out.weight":
+            return [] if spec.tie_word_embeddings else [(None, "lm_head", t)]
+        return []
+    parts = rest.split(".")
+    if kind not in ("weight", "bias"):
+        return []  # rotary inv_freq / mask buffers of older checkpoints
+    gb = "g" if kind == "weight" else "b"
+    sfx = _wb(kind)
+    if parts[0] == "input_layernorm":
+        return [(layer, f"norm1.{gb}", t)]
+    if parts[0] == "post_attention_layernorm":
+        return [(layer, f"norm2.{gb}", t)]
+    if parts[0] == "attention" and len(parts) == 3:
+        if parts[1] == "query_key_value":   # rows grouped per head: [head][q | k | v][head_dim]
+            g = t.reshape((spec.n_heads, 3, spec.head_dim) + tuple(t.shape[1:]))
+            flat = (spec.q_dim, ) + tuple(t.shape[1:])
+            return [(layer, f"attn.q{sfx}", g[:, 0].reshape(flat)), (layer, f"attn.k{sfx}", g[:, 1].reshape(flat)),
+                    (layer, f"attn.v{sfx}", g[:, 2].reshape(flat))]
+        if parts[1] == "dense":
+            return [(layer, f"attn.o{sfx}", t)]
+    if parts[0] == "mlp" and len(parts) == 3:
+        if parts[1] == "dense_h_to_4h":
+            return [(layer, f"mlp.up{sfx}", t)]
+        if parts[1] == "dense_4h_to_h":
+            return [(layer, f"mlp.down{sfx}", t)]
+    return []

@@ -79,14 +79,25 @@ def test_injected_encoder_matches_hf(name):
 
 def test_init_inference_kernel_inject_uses_containers():
     torch.manual_seed(0)
-    model = AutoModelForCausalLM.from_config(CAUSAL["gpt2"]()).eval().float()
     ids = torch.randint(1, 50, (1, 6))
-    with torch.no_grad():
-        want = model(ids).logits
-    engine = ds.init_inference(model, dtype=torch.float32, replace_with_kernel_inject=True)
-    assert engine.fused_layers == 2 and not engine.injected
-    with torch.no_grad():
-        torch.testing.assert_close(engine(ids).logits, want, rtol=1e-4, atol=1e-5)
+    # families / variants outside the ragged executor: block-by-block injection through the container policies
+    for name in ("gptneo", "bloom", "gpt2_scaled"):
+        model = AutoModelForCausalLM.from_config(CAUSAL[name]()).eval().float()
+        with torch.no_grad():
+            want = model(ids).logits
+        engine = ds.init_inference(model, dtype=torch.float32, replace_with_kernel_inject=True)
+        assert engine.fused_layers == 2 and not engine.injected, name
+        with torch.no_grad():
+            torch.testing.assert_close(engine(ids).logits, want, rtol=1e-4, atol=1e-5)
+    # GPT-2 / GPT-J / GPT-NeoX are lifted whole onto the ragged executor (paged KV, the sm_100a kernels on a GPU)
+    for name in ("gpt2", "gptj", "gptneox", "gptneox_sequential"):
+        model = AutoModelForCausalLM.from_config(CAUSAL[name]()).eval().float()
+        with torch.no_grad():
+            want = model(ids).logits
+        engine = ds.init_inference(model, dtype=torch.float32, replace_with_kernel_inject=True)
+        assert engine.injected and engine.fused_layers == 0 and engine.ragged_engine is not None, name
+        with torch.no_grad():
+            torch.testing.assert_close(engine(ids).logits, want, rtol=2e-4, atol=2e-5)
     with pytest.raises(ValueError, match="kernel injection is not available"):
         ds.init_inference(torch.nn.Linear(2, 2), dtype=torch.float32, replace_with_kernel_inject=True)
 
@@ -123,7 +134,7 @@ def test_checkpoint_json_into_meta_model_then_inject(tmp_path):
     save_mp_checkpoint_path writes a reloadable per-rank checkpoint (ref: inference/engine.py:366-475)."""
     import json
     torch.manual_seed(0)
-    cfg = CAUSAL["gpt2"]()
+    cfg = CAUSAL["gpt2_scaled"]()          # a variant that stays on the block-injection path
     src = AutoModelForCausalLM.from_config(cfg).eval().float()
     ids = torch.randint(1, 50, (1, 6))
     with torch.no_grad():

@@ -287,13 +287,27 @@ def _hf_model(kind):
         cfg = OPTConfig(vocab_size=2048, hidden_size=512, num_hidden_layers=3, ffn_dim=2048, num_attention_heads=8,
                         max_position_embeddings=1024, word_embed_proj_dim=512, do_layer_norm_before=True, dropout=0.0)
         return OPTForCausalLM(cfg).eval()
+    if kind == "gpt2":
+        from transformers import GPT2Config, GPT2LMHeadModel
+        return GPT2LMHeadModel(GPT2Config(vocab_size=2048, n_embd=512, n_layer=3, n_head=8, n_positions=1024, resid_pdrop=0.0,
+                                          embd_pdrop=0.0, attn_pdrop=0.0)).eval()
+    if kind == "gptj":
+        from transformers import GPTJConfig, GPTJForCausalLM
+        return GPTJForCausalLM(GPTJConfig(vocab_size=2048, n_embd=512, n_layer=3, n_head=8, n_positions=1024, rotary_dim=32,
+                                          resid_pdrop=0.0, embd_pdrop=0.0, attn_pdrop=0.0)).eval()
+    if kind == "gpt_neox":
+        from transformers import GPTNeoXConfig, GPTNeoXForCausalLM
+        return GPTNeoXForCausalLM(GPTNeoXConfig(vocab_size=2048, hidden_size=512, num_hidden_layers=3, num_attention_heads=4,
+                                                intermediate_size=2048, rotary_pct=0.25, max_position_embeddings=1024,
+                                                hidden_dropout=0.0, attention_dropout=0.0)).eval()
     from transformers import LlamaConfig, LlamaForCausalLM
     cfg = LlamaConfig(vocab_size=2048, hidden_size=512, intermediate_size=1408, num_hidden_layers=3, num_attention_heads=4,
                       num_key_value_heads=2, max_position_embeddings=1024)
     return LlamaForCausalLM(cfg).eval()
 
 
-@pytest.mark.parametrize("kind", ["opt", "llama"])
+# gpt2 / gptj / gpt_neox: the families the reference serves through its v1 transformer_inference op only
+@pytest.mark.parametrize("kind", ["opt", "llama", "gpt2", "gptj", "gpt_neox"])
 def test_v1_init_inference_kernel_inject_gpu(kind):
     """``init_inference(replace_with_kernel_inject=True)`` on the GPU (v1 API): the injected engine runs the sm_100a
     kernels, its logits track the HuggingFace model's fp32 logits for a prompt and for a continuation over the live KV

@@ -46,10 +46,19 @@ def _tiny(family):
         return T.Qwen2MoeForCausalLM(T.Qwen2MoeConfig(intermediate_size=256, moe_intermediate_size=64, shared_expert_intermediate_size=128,
                                                       num_key_value_heads=2, num_experts=4, num_experts_per_tok=2,
                                                       decoder_sparse_step=1, mlp_only_layers=[], **common))
+    if family == "gpt2":
+        return T.GPT2LMHeadModel(T.GPT2Config(n_embd=128, n_layer=2, n_head=4, vocab_size=300, n_positions=512))
+    if family == "gptj":
+        return T.GPTJForCausalLM(T.GPTJConfig(n_embd=128, n_layer=2, n_head=4, vocab_size=300, n_positions=512, rotary_dim=16))
+    if family == "gpt_neox":
+        return T.GPTNeoXForCausalLM(T.GPTNeoXConfig(intermediate_size=256, rotary_pct=0.5, use_parallel_residual=True, **common))
+    if family == "gpt_neox_sequential":
+        return T.GPTNeoXForCausalLM(T.GPTNeoXConfig(intermediate_size=256, rotary_pct=1.0, use_parallel_residual=False, **common))
     raise KeyError(family)
 
 
-FAMILIES = ["llama", "llama_mha_bias", "mistral", "qwen2", "opt", "falcon_mqa", "falcon_new", "phi", "phi3", "mixtral", "qwen2_moe"]
+FAMILIES = ["llama", "llama_mha_bias", "mistral", "qwen2", "opt", "falcon_mqa", "falcon_new", "phi", "phi3", "mixtral", "qwen2_moe",
+            "gpt2", "gptj", "gpt_neox", "gpt_neox_sequential"]
 
 
 @pytest.mark.parametrize("family", FAMILIES)
