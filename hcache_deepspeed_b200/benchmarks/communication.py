@@ -111,7 +111,8 @@ def run(args, out=sys.stdout) -> List[Dict]:
 def benchmark_parser() -> argparse.ArgumentParser:
     p = argparse.ArgumentParser(description="collective micro-benchmark (launch one process per rank, e.g. with bin/hds or torchrun)")
     p.add_argument("--op", default="all", choices=("all", ) + OPS)
-    p.add_argument("--backend", default="nccl" if torch.cuda.is_available() else "gloo", choices=["nccl", "gloo"])
+    p.add_argument("--backend", default="nccl" if torch.cuda.is_available() else "gloo", choices=["nccl", "gloo", "ccl"],
+                   help="ccl = gloo + this framework's shared-memory engine for host tensors")
     p.add_argument("--dtype", default="float32")
     p.add_argument("--minsize", type=int, default=1 << 10, help="smallest message in bytes")
     p.add_argument("--maxsize", type=int, default=1 << 26, help="largest message in bytes")
@@ -132,3 +133,7 @@ def main(argv=None) -> int:
         os.environ.setdefault("MASTER_PORT", "29577")
     run(args)
     return 0
+
+
+if __name__ == "__main__":
+    sys.exit(main())

@@ -156,16 +156,31 @@ def all_gather_coalesced_available() -> bool:
 # ---- collectives ---------------------------------------------------------------------------------------
 @timed_op
 def broadcast(tensor, src, group=None, async_op=False):
+    eng = _host_engine(group, tensor)
+    if eng is not None:
+        eng.broadcast(tensor, src if group is None else tdist.get_group_rank(group, src))
+        return _Done() if async_op else None
     return tdist.broadcast(tensor, src, group=group, async_op=async_op)
 
 
 @timed_op
 def all_gather(tensor_list, tensor, group=None, async_op=False):
+    eng = _host_engine(group, tensor)
+    if eng is not None and all(t.shape == tensor.shape and t.dtype == tensor.dtype for t in tensor_list):
+        flat = torch.empty((len(tensor_list), ) + tuple(tensor.shape), dtype=tensor.dtype)
+        eng.all_gather_into_tensor(flat, tensor)
+        for dst, src in zip(tensor_list, flat):
+            dst.copy_(src)
+        return _Done() if async_op else None
     return tdist.all_gather(tensor_list, tensor, group=group, async_op=async_op)
 
 
 @timed_op
 def all_gather_into_tensor(output_tensor, tensor, group=None, async_op=False):
+    eng = _host_engine(group, output_tensor, tensor)
+    if eng is not None:
+        eng.all_gather_into_tensor(output_tensor, tensor)
+        return _Done() if async_op else None
     return tdist.all_gather_into_tensor(output_tensor, tensor, group=group, async_op=async_op)
 
 
@@ -180,6 +195,10 @@ def all_gather_coalesced(output_tensors, input_tensors, group=None, async_op=Fal
 
 @timed_op
 def reduce_scatter_tensor(output_tensor, tensor, op=ReduceOp.SUM, group=None, async_op=False):
+    eng = _host_engine(group, tensor, output_tensor, op=op)
+    if eng is not None:
+        eng.reduce_scatter_tensor(output_tensor, tensor, op)
+        return _Done() if async_op else None
     return tdist.reduce_scatter_tensor(output_tensor, tensor, op=_op(op), group=group, async_op=async_op)
 
 
@@ -249,6 +268,10 @@ def scatter(tensor, scatter_list=None, src=0, group=None, async_op=False):
 
 @timed_op
 def barrier(group=None, async_op=False, device_ids=None):
+    eng = _host_engine(group) if device_ids is None else None
+    if eng is not None:
+        eng.barrier()
+        return _Done() if async_op else None
     return tdist.barrier(group=group, async_op=async_op, device_ids=device_ids)
 
 
@@ -262,8 +285,37 @@ def reduce(tensor, dst, op=ReduceOp.SUM, group=None, async_op=False):
     return tdist.reduce(tensor, dst, op=_op(op), group=group, async_op=async_op)
 
 
+class _Done:
+    """Work handle of a collective that has already completed (the shared-memory engine is synchronous)."""
+
+    def wait(self, timeout=None) -> bool:
+        return True
+
+    def is_completed(self) -> bool:
+        return True
+
+
+def _host_engine(group, *tensors, op=None, always: bool = False):
+    """The shared-memory engine attached to ``group`` when it can carry this call (contiguous CPU tensors, a dtype / op it
+    has), else None. General collectives use it only after a ``CCLBackend`` switched routing on; ``inference_all_reduce``
+    uses it whenever a group is attached."""
+    from . import shm
+    if not (always or shm.route_all_collectives):
+        return None
+    eng = shm.attached(group)
+    if eng is None or any(t.device.type != "cpu" or not t.is_contiguous() for t in tensors):
+        return None
+    if op is not None and not eng.supports(tensors[0], op):
+        return None
+    return eng
+
+
 @timed_op
 def all_reduce(tensor, op=ReduceOp.SUM, group=None, async_op=False):
+    eng = _host_engine(group, tensor, op=op)
+    if eng is not None:
+        eng.all_reduce(tensor, op)
+        return _Done() if async_op else None
     return tdist.all_reduce(tensor, op=_op(op), group=group, async_op=async_op)
 
 
@@ -272,10 +324,9 @@ def inference_all_reduce(tensor, op=ReduceOp.SUM, group=None):
     """Latency-oriented all-reduce of the inference path (ref: comm.py:506). On CUDA this is NCCL (NVLS when
     the switch offers it); the engine's own hot path bypasses it with fused GEMM epilogues. CPU fp32 / bf16 tensors
     go through the shared-memory engine once ``comm.shm.attach(group)`` has been called (ref: torch.py:160-166)."""
-    if tensor.device.type == "cpu" and op == ReduceOp.SUM:
-        from . import shm
-        if shm.usable(tensor, group):
-            return shm.attached(group).all_reduce(tensor)
+    eng = _host_engine(group, tensor, op=op, always=True)
+    if eng is not None:
+        return eng.all_reduce(tensor, op)
     return tdist.all_reduce(tensor, op=_op(op), group=group, async_op=False)
 
 
@@ -471,6 +522,12 @@ def init_distributed(dist_backend: Optional[str] = None, auto_mpi_discovery: boo
         local = int(os.environ["LOCAL_RANK"]) % max(1, torch.cuda.device_count())
         torch.cuda.set_device(local)
         kwargs["device_id"] = torch.device("cuda", local)
+    if dist_backend == "ccl":
+        # host collectives: gloo underneath, this framework's shared-memory engine for what it covers (comm/ccl.py)
+        from .ccl import CCLBackend
+        cdb = CCLBackend(rank=int(os.environ["RANK"]), world_size=int(os.environ["WORLD_SIZE"]), timeout=timeout,
+                         init_method=init_method)
+        return
     tdist.init_process_group(backend=dist_backend, init_method=init_method, timeout=timeout,
                              rank=int(os.environ["RANK"]), world_size=int(os.environ["WORLD_SIZE"]), **kwargs)
     cdb = True

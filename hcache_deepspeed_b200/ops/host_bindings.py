@@ -61,5 +61,17 @@ def declare(lib: ctypes.CDLL) -> None:
     lib.hds_shm_open.restype = P
     lib.hds_shm_allreduce.argtypes = [P, P, L, I]
     lib.hds_shm_allreduce.restype = I
+    lib.hds_shm_allreduce_op.argtypes = [P, P, L, I, I]
+    lib.hds_shm_allreduce_op.restype = I
+    lib.hds_shm_broadcast.argtypes = [P, P, L, I]
+    lib.hds_shm_broadcast.restype = I
+    lib.hds_shm_allgather.argtypes = [P, P, P, L]
+    lib.hds_shm_allgather.restype = I
+    lib.hds_shm_reduce_scatter.argtypes = [P, P, P, L, I, I]
+    lib.hds_shm_reduce_scatter.restype = I
+    lib.hds_shm_barrier.argtypes = [P]
+    lib.hds_shm_barrier.restype = I
+    lib.hds_shm_info.argtypes = [P, ctypes.POINTER(ctypes.c_int64)]
+    lib.hds_shm_info.restype = None
     lib.hds_shm_close.argtypes = [P, I]
     lib.hds_shm_close.restype = None

@@ -88,12 +88,20 @@ int hds_cpu_adagrad_step(float* params, const float* grads, float* exp_avg_sq, i
 int hds_cpu_lion_step(float* params, const float* grads, float* exp_avg, int64_t n, float lr, float beta1, float beta2,
                       float weight_decay, void* copy_out, int copy_dtype, int threads);
 
-/* ---- shared-memory all-reduce for intra-node CPU tensor parallelism (ref: csrc/cpu/comm/shm.cpp) ----------------
- * hds_shm_open: every rank of the group maps POSIX segment "/<name>" (world slots of slot_bytes) and waits until all
- * ranks have attached; NULL on failure. hds_shm_allreduce: in-place SUM over the group, dtype 0 = bf16 (fp32
- * accumulation), 2 = fp32; any numel (chunked by slot size). hds_shm_close unmaps (one rank passes unlink_segment). */
+/* ---- host collectives over one shared-memory segment, for the ranks of one node (ref: csrc/cpu/comm/shm.cpp, ccl.cpp) --
+ * hds_shm_open: every rank of the group maps POSIX segment "/<name>" (two banks of `world` slots of slot_bytes) and
+ * waits until all ranks have attached; NULL on failure. Every rank must then issue the same calls in the same order.
+ * dtype: 0 bf16, 1 fp16 (both accumulated in fp32), 2 fp32, 3 int32, 4 int64. op: 0 sum, 1 max, 2 min. Any size: messages
+ * are cut into slot-sized rounds. Return 0, -1 (bad argument) or -2 (a peer did not arrive within HDS_SHM_TIMEOUT_S,
+ * default 600). HDS_SHM_SIMD=off disables the AVX-512 kernels. hds_shm_close unmaps (one rank passes unlink_segment). */
 void* hds_shm_open(const char* name, int rank, int world, int64_t slot_bytes);
-int hds_shm_allreduce(void* handle, void* data, int64_t numel, int dtype);
+int hds_shm_allreduce(void* handle, void* data, int64_t numel, int dtype);                    /* in place, sum */
+int hds_shm_allreduce_op(void* handle, void* data, int64_t numel, int dtype, int op);         /* in place */
+int hds_shm_broadcast(void* handle, void* data, int64_t nbytes, int root);
+int hds_shm_allgather(void* handle, const void* in, void* out, int64_t nbytes_each);          /* out = [world][nbytes_each] */
+int hds_shm_reduce_scatter(void* handle, const void* in, void* out, int64_t numel_out, int dtype, int op); /* in = [world][numel_out] */
+int hds_shm_barrier(void* handle);
+void hds_shm_info(void* handle, int64_t* out4);  /* avx512 in use, rounds, one-exchange chunks, shard-per-rank chunks */
 void hds_shm_close(void* handle, int unlink_segment);
 
 #ifdef __cplusplus

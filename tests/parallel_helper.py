@@ -162,3 +162,108 @@ def shm_allreduce_worker(rank, world):
     out["name"] = g.name
     shm.detach()
     return out
+
+
+def ccl_backend_worker(rank, world):
+    """``init_distributed(dist_backend="ccl")``: every covered collective runs through the C++ shared-memory engine and
+    agrees with gloo; uncovered calls fall back; sub-groups get their own segment."""
+    import os
+    os.environ["HDS_SHM_SIMD"] = "off" if rank == -1 else os.environ.get("HDS_SHM_SIMD", "on")
+    import hcache_deepspeed_b200 as ds
+    from hcache_deepspeed_b200 import comm as dist
+    from hcache_deepspeed_b200.comm import comm as C, shm
+    from hcache_deepspeed_b200.comm.ccl import CCLBackend
+    from hcache_deepspeed_b200.comm.reduce_op import ReduceOp
+    ds.init_distributed(dist_backend="ccl")
+    be = C.cdb
+    assert isinstance(be, CCLBackend) and be.single_node and be.is_initialized()
+    eng = be.native_engine()
+    out = {"avx512": eng.info()["avx512"]}
+    gloo = torch.distributed.new_group(list(range(world)), backend="gloo")     # not attached: the oracle
+
+    def oracle_all_reduce(x, op):
+        y = x.clone().float() if x.dtype in (torch.float16, torch.bfloat16) else x.clone()
+        torch.distributed.all_reduce(y, op=op, group=gloo)
+        return y
+
+    errs = {}
+    for dtype in (torch.float32, torch.bfloat16, torch.float16, torch.int32, torch.int64):
+        for n in (1, 37, 4096 + 5, 300_001):      # one exchange, a partial vector, shard-per-rank, several rounds
+            torch.manual_seed(7 * rank + n)
+            x = (torch.randn(n) * 4).to(dtype) if dtype.is_floating_point else torch.randint(-50, 50, (n, ), dtype=dtype)
+            for op, top in ((ReduceOp.SUM, torch.distributed.ReduceOp.SUM), (ReduceOp.MAX, torch.distributed.ReduceOp.MAX),
+                            (ReduceOp.MIN, torch.distributed.ReduceOp.MIN)):
+                got = x.clone()
+                be.all_reduce(got, op=op)
+                want = oracle_all_reduce(x, top)
+                if dtype.is_floating_point:
+                    want = want.to(dtype)        # one rounding of the fp32 result
+                    e = float((got.float() - want.float()).abs().max())
+                    tol = {torch.float32: 1e-5, torch.bfloat16: 0.26, torch.float16: 0.04}[dtype] if op == ReduceOp.SUM else 0.0
+                    assert e <= tol, (dtype, n, op, e)
+                else:
+                    assert torch.equal(got, want), (dtype, n, op)
+    info = eng.info()
+    assert info["allreduce_one_exchange"] > 0 and info["allreduce_shard_per_rank"] > 0
+    # results are bit-identical on every rank (fixed summation order / one owner per shard)
+    x = torch.randn(70_001) * (rank + 1)
+    be.all_reduce(x)
+    ref = [torch.empty_like(x) for _ in range(world)]
+    torch.distributed.all_gather(ref, x, group=gloo)
+    assert all(torch.equal(r, ref[0]) for r in ref)
+
+    # broadcast / all-gather / reduce-scatter
+    for n in (5, 250_003):
+        b = torch.arange(n, dtype=torch.float64) * (1 if rank == world - 1 else -1)
+        be.broadcast(b, src=world - 1)
+        assert torch.equal(b, torch.arange(n, dtype=torch.float64))
+        mine = torch.full((n, ), rank, dtype=torch.int16)
+        flat = torch.empty(world * n, dtype=torch.int16)
+        be.all_gather_into_tensor(flat, mine)
+        assert torch.equal(flat.view(world, n), torch.arange(world, dtype=torch.int16)[:, None].expand(world, n))
+        lst = [torch.empty(n, dtype=torch.int16) for _ in range(world)]
+        be.all_gather(lst, mine)
+        assert all(int(t[0]) == r and int(t[-1]) == r for r, t in enumerate(lst))
+        torch.manual_seed(rank + n)
+        inp = torch.randn(world * n)
+        got = torch.empty(n)
+        be.reduce_scatter_tensor(got, inp)
+        want = inp.clone()
+        torch.distributed.all_reduce(want, group=gloo)
+        torch.testing.assert_close(got, want[rank * n:(rank + 1) * n], rtol=1e-5, atol=1e-5)
+        hb = (torch.randn(world * n) * 3).to(torch.bfloat16)
+        gb = torch.empty(n, dtype=torch.bfloat16)
+        be.reduce_scatter_tensor(gb, hb, op=ReduceOp.MAX)
+        wb = hb.float()
+        torch.distributed.all_reduce(wb, op=torch.distributed.ReduceOp.MAX, group=gloo)
+        assert torch.equal(gb.float(), wb[rank * n:(rank + 1) * n])
+    be.barrier()
+    for i in range(200):                               # back-to-back small calls: the two banks must not race
+        t = torch.full((33, ), float(rank + i))
+        dist.all_reduce(t)                             # the functional API is routed too
+        assert float(t[0]) == sum(r + i for r in range(world))
+    # not covered -> torch.distributed, and the counters say so
+    z = torch.ones(6, dtype=torch.float64)
+    be.all_reduce(z)
+    nc = torch.ones(4, 6)[:, ::2]
+    be.all_reduce(nc)
+    prod = torch.full((3, ), 2.0)
+    be.all_reduce(prod, op=ReduceOp.PRODUCT)
+    assert float(z[0]) == world and float(nc[0, 0]) == world and float(prod[0]) == 2.0**world
+    out["calls"] = dict(be.calls)
+    # a sub-group gets its own segment
+    if world >= 3:
+        sub = be.new_group([0, 2])
+        if rank in (0, 2):
+            assert be.native_engine(sub) is not None
+            t = torch.full((10, ), float(rank))
+            be.all_reduce(t, group=sub)
+            assert float(t[0]) == 2.0
+            b = torch.full((4, ), float(rank))
+            be.broadcast(b, src=2, group=sub)          # global rank 2 = group rank 1
+            assert float(b[0]) == 2.0
+    names = [eng.name]
+    be.close()
+    assert shm.attached() is None and not shm.route_all_collectives
+    out["name"] = names[0]
+    return out

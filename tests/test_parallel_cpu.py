@@ -125,3 +125,21 @@ def test_torch_backend_object_2ranks():
     res = run_distributed(_torch_backend_worker, 2)
     for r in res:
         assert r["sum"] == [3.0] * 4 and r["gathered"] == [0.0, 0.0, 1.0, 1.0] and r["size"] == 2 and r["msg"] == 16
+
+
+@pytest.mark.parametrize("world,simd", [(2, "on"), (3, "on"), (4, "off")])
+def test_ccl_backend_host_collectives(world, simd, monkeypatch):
+    """The host back end (``dist_backend="ccl"``): all-reduce sum/max/min over five dtypes, broadcast, all-gather,
+    reduce-scatter and barrier through the C++ shared-memory engine (both all-reduce shapes, AVX-512 and portable
+    kernels) against gloo; uncovered calls fall back to torch.distributed."""
+    import os
+    from tests.parallel_helper import ccl_backend_worker
+    monkeypatch.setenv("HDS_SHM_SIMD", simd)
+    res = run_distributed(ccl_backend_worker, world)
+    for r in res:
+        calls = r["calls"]
+        assert calls["all_reduce.native"] >= 60 and calls["all_reduce.torch"] == 3, calls
+        assert calls["broadcast.native"] == 2 and calls["reduce_scatter_tensor.native"] == 4 and calls["barrier.native"] == 1, calls
+        if simd == "off":
+            assert r["avx512"] == 0
+    assert not os.path.exists("/dev/shm/" + res[0]["name"])
