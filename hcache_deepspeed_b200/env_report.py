@@ -22,11 +22,24 @@ def op_report(verbose: bool = True):
     print(f"{'op name':<45}{'built':<12}{'buildable here':<12}")
     for name, built, can in rows:
         print(f"{name:<45}{OKAY if built else NO:<21}{OKAY if can else NO}")
-    try:
-        from .io import gds_available
-        print(f"{'GPUDirect Storage (libcufile)':<45}{OKAY if gds_available() else NO}")
-    except Exception:
-        pass
+    # one line per op builder: pre-built in the in-tree library / can be JIT-built here, and why not if not
+    from .ops.op_builder import ALL_OPS
+    print("-" * 74)
+    print(f"{'op builder':<30}{'pre-built':<12}{'compatible':<12}translation units")
+    for name, b in sorted(ALL_OPS.items()):
+        problems = b.compatibility_problems()
+        units = ", ".join(p.name for p in b.all_sources()) or "(torch formulation)"
+        print(f"{name:<30}{OKAY if b.installed() else NO:<21}{OKAY if not problems else NO:<21}{units}")
+        if verbose:
+            for w in problems:
+                print(f"{'':<30}{YELLOW}{w}{END}")
+        rows.append((name, b.installed(), not problems))
+    if os.environ.get("HDS_REPORT_GDS", "0") == "1":      # opens the cuFile driver in a child process: slow where it blocks
+        try:
+            from .io import gds_available
+            print(f"{'GPUDirect Storage (libcufile)':<45}{OKAY if gds_available() else NO}")
+        except Exception:
+            pass
     return rows
 
 

@@ -2,6 +2,7 @@
 re-sharding, sparse-attention layouts, Evoformer attention, accelerator / op-builder surfaces, data sampling."""
 import math
 import os
+import subprocess
 import types
 
 import numpy as np
@@ -716,3 +717,64 @@ def test_launcher_environment_discovery(monkeypatch):
     assert (os.environ["RANK"], os.environ["LOCAL_RANK"], os.environ["WORLD_SIZE"], os.environ["MASTER_ADDR"]) == \
         ("2", "0", "4", "algo-1")
     clean()
+
+
+def test_op_builder_probes_jit_and_dependency_tables(tmp_path, monkeypatch):
+    """Per-op builders (ref: op_builder/builder.py:523-607): compatibility probes, a JIT build of one host op and one
+    CUDA op into a hashed cache, and DEPENDS tables that really close over the symbols their sources use."""
+    import ctypes
+    from hcache_deepspeed_b200.ops import build
+    from hcache_deepspeed_b200.ops.op_builder import (ALL_OPS, OpBuildError, QuantizerBuilder, ShareMemCommBuilder, has_function,
+                                                      has_header, nvcc_knows_sm100a, nvcc_version)
+    from hcache_deepspeed_b200.ops.op_builder.builder import unresolved_symbols
+    build.build_all(verbose=False)
+    assert nvcc_version() >= (12, 8) and nvcc_knows_sm100a()
+    assert has_header("linux/aio_abi.h") and not has_header("no_such_header_hds.h")
+    assert has_function("shm_open", headers=("sys/mman.h", ), libs=("rt", )) and not has_function("hds_no_such_fn")
+    for name, b in ALL_OPS.items():
+        assert b.is_compatible() and b.installed(), (name, b.error_log)
+        assert all(p.exists() for p in b.all_sources()), name
+        assert unresolved_symbols(b) == [], (name, unresolved_symbols(b))
+    incomplete = type("Broken", (QuantizerBuilder, ), {"NAME": "broken", "SOURCES": ("gemm.cu", ), "DEPENDS": ()})()
+    assert any("tp_take_armed" in s for s in unresolved_symbols(incomplete))
+
+    monkeypatch.setenv("HDS_JIT_DIR", str(tmp_path / "jit"))
+    monkeypatch.setenv("HDS_FORCE_JIT", "1")
+    shm_b = ShareMemCommBuilder()
+    h0 = shm_b.build_hash()
+    monkeypatch.setenv("HDS_BUILD_OPS", "0")
+    with pytest.raises(OpBuildError, match="HDS_BUILD_OPS=0"):
+        shm_b.load(verbose=False)
+    monkeypatch.delenv("HDS_BUILD_OPS")
+    lib = shm_b.load(verbose=False)
+    assert shm_b.jit_path().exists() and shm_b.jit_path().name == f"deepspeed_shm_comm-{h0}.so"
+    # the JIT-built object works on its own: a one-rank group reduces to itself
+    lib.hds_shm_open.restype = ctypes.c_void_p
+    lib.hds_shm_open.argtypes = [ctypes.c_char_p, ctypes.c_int, ctypes.c_int, ctypes.c_int64]
+    lib.hds_shm_allreduce.argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_int64, ctypes.c_int]
+    lib.hds_shm_close.argtypes = [ctypes.c_void_p, ctypes.c_int]
+    name = f"hds_jit_test_{os.getpid()}".encode()
+    g = lib.hds_shm_open(name, 0, 1, 4096)
+    assert g
+    x = torch.arange(3000, dtype=torch.float32)
+    assert lib.hds_shm_allreduce(g, x.data_ptr(), x.numel(), 2) == 0 and float(x[-1]) == 2999.0
+    lib.hds_shm_close(g, 1)
+    # a different flag set is a different artefact; the old one is dropped
+    monkeypatch.setattr(ShareMemCommBuilder, "cxx_args", lambda self: ["-O1", "-std=c++17", "-fPIC", "-pthread"])
+    b2 = ShareMemCommBuilder()
+    assert b2.build_hash() != h0
+    b2.load(verbose=False)
+    assert [p.name for p in (tmp_path / "jit").glob("deepspeed_shm_comm-*.so")] == [b2.jit_path().name]
+    # one CUDA op cross-compiled for sm_100a on its own
+    q = QuantizerBuilder()
+    qlib = q.load(verbose=False)
+    assert hasattr(qlib, "hds_quantize_int") and not hasattr(qlib, "hds_gemm")
+    sass = subprocess.run(["cuobjdump", "-lelf", str(q.jit_path())], stdout=subprocess.PIPE, text=True).stdout
+    assert "sm_100a" in sass
+    # a missing tool chain is reported, and a pre-built library still makes the op usable
+    monkeypatch.delenv("HDS_FORCE_JIT")
+    monkeypatch.setenv("NVCC", "/nonexistent/nvcc")
+    q2 = QuantizerBuilder()
+    assert q2.is_compatible() and any("nvcc not found" in w for w in q2.error_log)
+    with pytest.raises(OpBuildError, match="nvcc not found"):
+        q2.jit_build(verbose=False)
