@@ -374,7 +374,7 @@ class DeepSpeedEngine(torch.nn.Module):
                 dynamic_loss_args=self._config.dynamic_loss_scale_args, dp_process_group=self.data_parallel_group,
                 param_persistence_threshold=zc.param_persistence_threshold, offload_optimizer_config=zc.offload_optimizer,
                 prefetch_bucket_size=zc.prefetch_bucket_size, max_live_parameters=zc.max_live_parameters,
-                aio_config=self._config.aio_config,
+                max_reuse_distance=zc.max_reuse_distance, aio_config=self._config.aio_config,
                 offload_param_config=zc.offload_param, mpu=self.mpu, clip_grad=clip,
                 gradient_predivide_factor=self.gradient_predivide_factor(), verbose=self.global_rank == 0, **extra)
         elif self.fp16_enabled():

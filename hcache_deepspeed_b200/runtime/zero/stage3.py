@@ -49,13 +49,18 @@ class DeepSpeedZeRoOffload:
         # ``prefetch_bucket_size`` elements, while the current module computes. A diverging order drops the trace.
         self.prefetch_bucket_size = int(prefetch_bucket_size)
         self.max_live_parameters = int(max_live_parameters) or 2 ** 62
+        # a parameter whose next use (by the trace) is fewer than this many fetched elements away is not released in
+        # between: the last layers' weights survive from forward into backward instead of being gathered twice
+        self.max_reuse_distance = int(max_reuse_distance)
+        self._uses = None                       # id(param) -> sorted trace positions; built with the trace
+        self._cum_numel: List[int] = []         # elements fetched by trace events [0, i)
         self.trace: List[tuple] = []            # [(module, phase)] of one forward(+backward)
         self.trace_complete = False
         self.prefetch_plan: Optional[List[List[torch.nn.Parameter]]] = None   # set by compile passes; else derived
         self.event_times: List[float] = []      # perf_counter at each recorded event (profile for the passes)
         self._recording: List[tuple] = []
         self._pos = 0
-        self.stats = {"prefetched": 0, "trace_invalidations": 0}
+        self.stats = {"prefetched": 0, "trace_invalidations": 0, "kept_for_reuse": 0}
         self._install(module)
 
     @staticmethod
@@ -97,6 +102,37 @@ class DeepSpeedZeRoOffload:
 
     def reset_trace(self):
         self.trace, self.trace_complete, self.prefetch_plan, self._recording, self._pos = [], False, None, [], 0
+        self._uses = None
+
+    def _index_uses(self):
+        uses, cum, total = {}, [0], 0
+        for i, (m, _) in enumerate(self.trace):
+            for p in self._own_params(m):
+                uses.setdefault(id(p), []).append(i)
+                if not p.ds_persist:
+                    total += p.ds_numel
+            cum.append(total)
+        self._uses, self._cum_numel = uses, cum
+
+    def _reused_soon(self, p) -> bool:
+        """True when the recorded order says ``p`` is needed again within ``max_reuse_distance`` fetched elements of the
+        current position (and keeping it does not break the live-parameter cap)."""
+        if self.max_reuse_distance <= 0 or not self.trace_complete or not self.trace:
+            return False
+        if self._uses is None:
+            self._index_uses()
+        import bisect
+        where = self._uses.get(id(p))
+        if not where:
+            return False
+        k = bisect.bisect_left(where, self._pos)
+        if k == len(where):
+            return False                        # not used again before the iteration ends
+        if self.trace[where[k]][1] == "bwd" and not torch.is_grad_enabled():
+            return False                        # evaluation: the recorded backward will not come
+        if self._cum_numel[where[k]] - self._cum_numel[min(self._pos, len(self.trace))] > self.max_reuse_distance:
+            return False
+        return self._live_numel() <= self.max_live_parameters
 
     def _live_numel(self) -> int:
         zp = self.__dict__.get("_zero_params")
@@ -166,6 +202,9 @@ class DeepSpeedZeRoOffload:
         for p in self._own_params(m):
             p.ds_active_sub_modules.discard(id(m))
             if not p.ds_active_sub_modules and not p.ds_persist:
+                if self._reused_soon(p):
+                    self.stats["kept_for_reuse"] += 1
+                    continue
                 _partition_param(p, has_been_updated=False)
 
     def destroy(self):
@@ -216,6 +255,7 @@ class DeepSpeedZeroOptimizer_Stage3:
         self.parameter_offload = DeepSpeedZeRoOffload(module, dp_process_group=dp_process_group,
                                                       prefetch_bucket_size=prefetch_bucket_size,
                                                       max_live_parameters=max_live_parameters,
+                                                      max_reuse_distance=max_reuse_distance,
                                                       param_persistence_threshold=param_persistence_threshold,
                                                       offload_param_config=offload_param_config, mpu=mpu, dtype=None)
         self.parameter_offload.reduce_fn = self._reduce_ready_grads

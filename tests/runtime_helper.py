@@ -52,6 +52,8 @@ def zero_worker(rank, world, stage, steps, gas, offload, dtype_name, ckpt_dir):
     cfg = {"train_micro_batch_size_per_gpu": micro, "gradient_accumulation_steps": gas,
            "optimizer": {"type": "AdamW", "params": {"lr": 1e-2, "weight_decay": 0.0}},
            "zero_optimization": {"stage": stage, "stage3_param_persistence_threshold": 0}, "steps_per_print": 1000}
+    if os.environ.get("HDS_TEST_Z3_REUSE") is not None:
+        cfg["zero_optimization"]["stage3_max_reuse_distance"] = int(os.environ["HDS_TEST_Z3_REUSE"])
     if offload == "nvme":
         import tempfile
         cfg["zero_optimization"]["offload_optimizer"] = {"device": "nvme", "pipeline_read": True, "pipeline_write": True,
@@ -106,6 +108,7 @@ def zero_worker(rank, world, stage, steps, gas, offload, dtype_name, ckpt_dir):
             out["prefetch_stats"] = dict(engine.optimizer.parameter_offload.stats)
             out["persistent"] = sum(1 for p in engine.module.parameters() if p.ds_persist)
     if stage == 3:
+        out["offload_stats"] = dict(engine.optimizer.parameter_offload.stats)
         from hcache_deepspeed_b200.runtime.zero import GatheredParameters
         sd = {}
         for n, p in engine.module.named_parameters():

@@ -224,6 +224,29 @@ def test_zero3_leaf_module_2ranks(monkeypatch):
             torch.testing.assert_close(r["state"][k], v, rtol=2e-4, atol=2e-5)
 
 
+@pytest.mark.parametrize("distance", [0, 100, 10 ** 9])
+def test_zero3_max_reuse_distance_2ranks(monkeypatch, distance):
+    """stage3_max_reuse_distance: a parameter the recorded order needs again within that many fetched elements is not
+    released in between (ref: partitioned_param_coordinator.py release_sub_module). Results never change."""
+    monkeypatch.setenv("HDS_TEST_Z3_REUSE", str(distance))
+    steps, world = 4, 2
+    want, want_state = reference_run(steps=steps, global_bs=4 * world)
+    res = run_distributed(zero_worker, world, 3, steps, 1, False, "fp32", None)
+    kept = [r["offload_stats"]["kept_for_reuse"] for r in res]
+    for r in res:
+        for k, v in want_state.items():
+            torch.testing.assert_close(r["state"][k], v, rtol=2e-4, atol=2e-5)
+    if distance == 0:
+        assert kept == [0, 0]
+    else:
+        assert all(k > 0 for k in kept)                 # the head's weights at least survive from forward into backward
+    test_zero3_max_reuse_distance_2ranks.kept = getattr(test_zero3_max_reuse_distance_2ranks, "kept", {})
+    test_zero3_max_reuse_distance_2ranks.kept[distance] = kept[0]
+    seen = test_zero3_max_reuse_distance_2ranks.kept
+    if 100 in seen and 10 ** 9 in seen:
+        assert seen[100] < seen[10 ** 9]                # a short distance keeps fewer parameters than an unbounded one
+
+
 def test_zero3_nvme_optimizer_swapper_2ranks(tmp_path):
     """ZeRO-Infinity: fp32 masters + Adam moments live in files between steps (pipelined swapper); same training
     result, checkpoint resume included."""
