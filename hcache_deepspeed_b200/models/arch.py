@@ -30,7 +30,9 @@ class ArchSpec:
     act: str = "silu"
     gated_mlp: bool = True
     # positions
-    pos_emb: str = "rope"  # "rope" | "learned" | "none"
+    pos_emb: str = "rope"  # "rope" | "learned" | "alibi" | "none"
+    alibi_scale: float = 1.0  # multiplies the ALiBi slopes (Falcon adds the bias BEFORE its 1/sqrt(d): scale = 1/sqrt(d))
+    embed_norm: bool = False  # LayerNorm on the token embeddings (Bloom's word_embeddings_layernorm)
     rope_theta: float = 10000.0
     rotary_dim: Optional[int] = None  # None = head_dim
     rope_scaling: Optional[Dict[str, Any]] = None
@@ -187,13 +189,12 @@ def _falcon(cfg) -> ArchSpec:
         nkv = _get(cfg, "num_kv_heads", default=nh)
     else:
         nkv = 1 if _get(cfg, "multi_query", default=True) else nh
-    if _get(cfg, "alibi", default=False):
-        raise ValueError("ALiBi Falcon variants are not supported")
+    alibi = bool(_get(cfg, "alibi", default=False))
     return ArchSpec(
         model_type="falcon", n_layers=_get(cfg, "num_hidden_layers"), hidden=h, n_heads=nh, n_kv_heads=nkv,
         head_dim=h // nh, intermediate=_get(cfg, "ffn_hidden_size", default=4 * h), vocab=_get(cfg, "vocab_size"),
-        norm="layer", norm_eps=_get(cfg, "layer_norm_epsilon", default=1e-5), act="gelu", gated_mlp=False, pos_emb="rope",
-        rope_theta=_rope_theta(cfg), max_positions=_get(cfg, "max_position_embeddings", default=2048),
+        norm="layer", norm_eps=_get(cfg, "layer_norm_epsilon", default=1e-5), act="gelu", gated_mlp=False,
+        pos_emb="alibi" if alibi else "rope", alibi_scale=(h // nh) ** -0.5 if alibi else 1.0, rope_theta=_rope_theta(cfg), max_positions=_get(cfg, "max_position_embeddings", default=2048),
         qkv_bias=bool(_get(cfg, "bias", default=False)), attn_out_bias=bool(_get(cfg, "bias", default=False)),
         mlp_bias=bool(_get(cfg, "bias", default=False)), norm_bias=True,
         parallel_residual=bool(_get(cfg, "parallel_attn", default=True)), parallel_two_norms=new_arch,
@@ -281,6 +282,20 @@ def _gpt_neox(cfg) -> ArchSpec:
         qkv_bias=bool(_get(cfg, "attention_bias", default=True)), attn_out_bias=bool(_get(cfg, "attention_bias", default=True)),
         mlp_bias=True, norm_bias=True, parallel_residual=par, parallel_two_norms=par,
         tie_word_embeddings=bool(_get(cfg, "tie_word_embeddings", default=False)))
+
+
+@register_arch("bloom")
+def _bloom(cfg) -> ArchSpec:
+    h = _get(cfg, "hidden_size", "n_embed")
+    nh = _get(cfg, "n_head", "num_attention_heads")
+    if _get(cfg, "apply_residual_connection_post_layernorm", default=False):
+        raise ValueError("Bloom variants with the residual taken after the LayerNorm are not supported")
+    return ArchSpec(
+        model_type="bloom", n_layers=_get(cfg, "n_layer", "num_hidden_layers"), hidden=h, n_heads=nh, n_kv_heads=nh,
+        head_dim=h // nh, intermediate=4 * h, vocab=_get(cfg, "vocab_size"), norm="layer",
+        norm_eps=_get(cfg, "layer_norm_epsilon", default=1e-5), act="gelu_tanh", gated_mlp=False, pos_emb="alibi",
+        max_positions=_get(cfg, "seq_length", "max_position_embeddings", default=2048), qkv_bias=True, attn_out_bias=True,
+        mlp_bias=True, norm_bias=True, embed_norm=True, tie_word_embeddings=True)
 
 
 @register_arch("mixtral")

@@ -381,3 +381,43 @@ def map_gpt_neox(name: str, t: torch.Tensor, spec: ArchSpec) -> List[Piece]:
         if parts[1] == "dense_4h_to_h":
             return [(layer, f"mlp.down{sfx}", t)]
     return []
+
+
+# ---------------------------------------------------------------------------------------------------
+@register_mapper("bloom")
+def map_bloom(name: str, t: torch.Tensor, spec: ArchSpec) -> List[Piece]:
+    """Bloom (ref: module_inject/containers/bloom.py): ALiBi attention, LayerNorm on the embeddings, fused QKV with rows
+    grouped per head [head][q | k | v][head_dim]."""
+    layer, rest = _split_layer(name)
+    kind = name.split(".")[-1]
+    if kind not in ("weight", "bias"):
+        return []
+    gb = "g" if kind == "weight" else "b"
+    if layer is None:
+        if name.endswith("word_embeddings.weight"):
+            return [(None, "embed", t)]
+        if "word_embeddings_layernorm." in name:
+            return [(None, f"embed_norm.{gb}", t)]
+        if ".ln_f." in name or name.startswith("ln_f."):
+            return [(None, f"final_norm.{gb}", t)]
+        return []  # lm_head is tied
+    parts = rest.split(".")
+    sfx = _wb(kind)
+    if parts[0] == "input_layernorm":
+        return [(layer, f"norm1.{gb}", t)]
+    if parts[0] == "post_attention_layernorm":
+        return [(layer, f"norm2.{gb}", t)]
+    if parts[0] == "self_attention" and len(parts) == 3:
+        if parts[1] == "query_key_value":
+            g = t.reshape((spec.n_heads, 3, spec.head_dim) + tuple(t.shape[1:]))
+            flat = (spec.q_dim, ) + tuple(t.shape[1:])
+            return [(layer, f"attn.q{sfx}", g[:, 0].reshape(flat)), (layer, f"attn.k{sfx}", g[:, 1].reshape(flat)),
+                    (layer, f"attn.v{sfx}", g[:, 2].reshape(flat))]
+        if parts[1] == "dense":
+            return [(layer, f"attn.o{sfx}", t)]
+    if parts[0] == "mlp" and len(parts) == 3:
+        if parts[1] == "dense_h_to_4h":
+            return [(layer, f"mlp.up{sfx}", t)]
+        if parts[1] == "dense_4h_to_h":
+            return [(layer, f"mlp.down{sfx}", t)]
+    return []

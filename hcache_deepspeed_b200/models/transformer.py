@@ -118,6 +118,10 @@ class RaggedTransformer:
         self.inv_freq = None
         if spec.pos_emb == "rope":
             self.inv_freq = self._make_inv_freq().to(self.device)
+        self.alibi = None
+        if spec.pos_emb == "alibi":      # slopes of THIS rank's query heads; the kernels add slope * (key - query position)
+            slopes = ref.alibi_slopes(spec.n_heads) * float(spec.alibi_scale)
+            self.alibi = slopes[torch.tensor(self.info.q_heads)].contiguous().to(self.device)
         self._alloc_buffers()
 
     # ------------------------------------------------------------------------------------------------
@@ -162,6 +166,7 @@ class RaggedTransformer:
         self._tp_scatter_ok = self._tp_fused and not s.is_moe and not s.parallel_residual and s.final_norm
         sym = (lambda *shape, dtype=dt: self.comm.alloc_symmetric(shape, dtype)) if self._tp_scatter_ok else buf
         self.residual = buf(T, H)
+        self.embed_tmp = buf(T, H) if s.embed_norm else None     # raw embeddings before their LayerNorm (Bloom)
         self.xn = sym(T, H)
         self.xn2 = sym(T, H)
         self.latent_buf = sym(s.n_layers, T, H) if self.capture_enabled else None
@@ -474,7 +479,12 @@ class RaggedTransformer:
             raise RuntimeError("hidden-state capture was disabled when the model was built")
         pos, slot = batch.tok_pos(), batch.tok_slot()
         resid = self.residual[:T]
-        ops.embed(batch.input_ids(), w.embed, resid, pos_weight=w.pos_embed, tok_pos=pos, pos_offset=s.learned_pos_offset)
+        if w.embed_norm_g is not None:   # Bloom: the residual stream starts from the normalised embeddings
+            raw = self.embed_tmp[:T]
+            ops.embed(batch.input_ids(), w.embed, raw, pos_weight=w.pos_embed, tok_pos=pos, pos_offset=s.learned_pos_offset)
+            ops.norm(raw, w.embed_norm_g, resid, beta=w.embed_norm_b, eps=s.norm_eps, layer_norm=True)
+        else:
+            ops.embed(batch.input_ids(), w.embed, resid, pos_weight=w.pos_embed, tok_pos=pos, pos_offset=s.learned_pos_offset)
         ln = s.norm == "layer"
         pending = None
         kv = self._state_manager
@@ -496,7 +506,7 @@ class RaggedTransformer:
                                    comm=self.comm, tp_wait=self._take_tp_wait())
             attn = self.attn_buf[:T]
             ops.attention(self.q_buf[:T], attn, kv_layer, batch, self.n_q, self.n_kv, self.d, self.scale,
-                          ws_small=self.ws_small, ws_large=self.ws_large)
+                          ws_small=self.ws_small, ws_large=self.ws_large, alibi=self.alibi)
             if s.parallel_residual:
                 xm = xn
                 if two_norms:

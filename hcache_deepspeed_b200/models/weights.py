@@ -70,6 +70,8 @@ class LayerWeights:
 class ModelWeights:
     embed: Optional[torch.Tensor] = None
     pos_embed: Optional[torch.Tensor] = None
+    embed_norm_g: Optional[torch.Tensor] = None     # LayerNorm applied to the token embeddings (Bloom)
+    embed_norm_b: Optional[torch.Tensor] = None
     final_norm_g: Optional[torch.Tensor] = None
     final_norm_b: Optional[torch.Tensor] = None
     lm_head: Optional[torch.Tensor] = None
@@ -78,7 +80,7 @@ class ModelWeights:
 
     def named_tensors(self) -> Dict[str, torch.Tensor]:
         out = {}
-        for k in ("embed", "pos_embed", "final_norm_g", "final_norm_b", "lm_head", "lm_head_b"):
+        for k in ("embed", "pos_embed", "embed_norm_g", "embed_norm_b", "final_norm_g", "final_norm_b", "lm_head", "lm_head_b"):
             v = getattr(self, k)
             if v is not None:
                 out[k] = v
@@ -290,6 +292,9 @@ class WeightAssembler:
         o.embed = self._to(self.top["embed"])
         o.pos_embed = self._to(self.top.get("pos_embed"))
         o.final_norm_g, o.final_norm_b = self._to(self.top.get("final_norm.g")), self._to(self.top.get("final_norm.b"))
+        o.embed_norm_g, o.embed_norm_b = self._to(self.top.get("embed_norm.g")), self._to(self.top.get("embed_norm.b"))
+        if self.spec.embed_norm and o.embed_norm_g is None:
+            raise ValueError("checkpoint has no embedding LayerNorm but the architecture needs one")
         if "lm_head" in self.top:
             o.lm_head = self._to(self.top["lm_head"])
         else:  # tied embeddings: the head is this rank's vocabulary slice of the embedding
@@ -332,6 +337,8 @@ def random_weights(spec: ArchSpec, tp_rank: int = 0, tp_size: int = 1, dtype: to
     mw.embed = rnd((spec.vocab, H), g_shared)
     if spec.pos_emb == "learned":
         mw.pos_embed = rnd((spec.max_positions + spec.learned_pos_offset, H), g_shared)
+    if spec.embed_norm:
+        mw.embed_norm_g, mw.embed_norm_b = ones(H), rnd((H, ), g_shared)
     if spec.final_norm:
         mw.final_norm_g = ones(H)
         mw.final_norm_b = rnd((H, ), g_shared) if spec.norm_bias else None

@@ -45,6 +45,7 @@ struct PrefillArgs {
     int32_t* tickets;   // [n_items][n_q_heads][4 quadrants][2 halves], zero between calls
     float* ws_ml;       // [n_items][n_q_heads][n_splits][128][2]
     float* ws_o;        // [n_items][n_q_heads][n_splits][128][D]
+    const float* alibi; // [n_q_heads] ALiBi slopes (natural-log units) or nullptr
 };
 
 __device__ __forceinline__ float ex2_approx(float x) {
@@ -266,6 +267,15 @@ paged_attn_prefill_kernel(const __grid_constant__ CUtensorMap tmap_q, const __gr
             tc_fence_before();
             __syncwarp();
             if (lane == 0) mbar_arrive(s_empty);
+            if (a.alibi != nullptr) {
+                // ALiBi: raw score += slope * (key - query position), expressed in raw-score units so that the scaling below
+                // stays one multiply-add per element (kernel-uniform branch; slopes differ per row only in packed mode)
+                const float sl = a.alibi[r_head] * 1.4426950408889634f / a.scale_log2;
+                const float d0 = static_cast<float>(tok0 - q_pos);
+#pragma unroll
+                for (int j = 0; j < HC; ++j)
+                    sr[j] = __float_as_uint(fmaf(sl, d0 + static_cast<float>(j), __uint_as_float(sr[j])));
+            }
             float tmax = -INFINITY;
             if (need_mask) {
 #pragma unroll
@@ -288,7 +298,8 @@ paged_attn_prefill_kernel(const __grid_constant__ CUtensorMap tmap_q, const __gr
             const float m_cand = fmaxf(m_run, tmax * a.scale_log2);
             const bool grow = (m_cand > m_run + kRescaleThreshold) || (m_run == -INFINITY && m_cand != -INFINITY);
             const float m_new = grow ? m_cand : m_run;
-            const float alpha = (!grow || m_run == -INFINITY) ? (grow ? 0.0f : 1.0f) : ex2_approx(m_run - m_new);
+            const bool fresh = (m_run == -INFINITY);   // nothing accumulated for this row yet
+            const float alpha = (!grow || fresh) ? (grow ? 0.0f : 1.0f) : ex2_approx(m_run - m_new);
             const float m_sub = (m_new == -INFINITY) ? 0.0f : m_new;  // fully masked row: exp2(-inf - 0) = 0
             float ps0 = 0.0f, ps1 = 0.0f;
             uint32_t packed[HC / 2];
@@ -306,7 +317,9 @@ paged_attn_prefill_kernel(const __grid_constant__ CUtensorMap tmap_q, const __gr
             if (ti > 0) {
                 mbar_wait(o_full, (ti - 1) & 1);
                 tc_fence_after();
-                const bool rescale = grow && alpha != 0.0f;  // alpha == 0: nothing accumulated for this row yet
+                // (alpha may underflow to exactly 0 when the maximum jumps by > 126 log2 units, e.g. under a steep ALiBi
+                // slope: the stale accumulation must then still be wiped, so "fresh" is tracked separately)
+                const bool rescale = grow && !fresh;
                 if (__any_sync(0xffffffffu, rescale)) {
                     const float f = rescale ? alpha : 1.0f;
 #pragma unroll
@@ -500,9 +513,11 @@ static int attention_tc_impl(bool packed, const void* q, void* out, const void* 
                 "paged_attention_prefill: block_size must be 16/32/64/128");
     HDS_REQUIRE(n_kv_heads > 0 && n_q_heads % n_kv_heads == 0, "paged_attention_prefill: n_q_heads % n_kv_heads != 0");
     HDS_REQUIRE(dtype == 0 || dtype == 1, "paged_attention_prefill: dtype must be 0 (bf16) or 1 (fp16)");
+    const float* alibi = attn_take_alibi();
     if (n_items == 0) return HDS_OK;
     PrefillArgs a;
     memset(&a, 0, sizeof(a));
+    a.alibi = alibi;
     a.out = out;
     a.block_tables = block_tables;
     a.items = items;
@@ -546,7 +561,7 @@ static int attention_tc_impl(bool packed, const void* q, void* out, const void* 
     if (packed)
         return dtype == 0 ? launch_prefill<128, true, true>(tq, tkv, a, n_items, s)
                           : launch_prefill<128, false, true>(tq, tkv, a, n_items, s);
-    if (head_dim == 128 && block_size <= 64 && prefill64_enabled())
+    if (head_dim == 128 && block_size <= 64 && alibi == nullptr && prefill64_enabled())   // the 64-key variant has no ALiBi term
         return dtype == 0 ? launch_prefill64<true>(tq, tkv, a, n_items, s) : launch_prefill64<false>(tq, tkv, a, n_items, s);
     if (head_dim == 128)
         return dtype == 0 ? launch_prefill<128, true>(tq, tkv, a, n_items, s)

@@ -207,7 +207,8 @@ paged_attn_prefill64_kernel(const __grid_constant__ CUtensorMap tmap_q, const __
             const float m_cand = fmaxf(m_run, tmax * a.scale_log2);
             const bool grow = (m_cand > m_run + kRescaleThreshold) || (m_run == -INFINITY && m_cand != -INFINITY);
             const float m_new = grow ? m_cand : m_run;
-            const float alpha = (!grow || m_run == -INFINITY) ? (grow ? 0.0f : 1.0f) : ex2_approx(m_run - m_new);
+            const bool fresh = (m_run == -INFINITY);   // nothing accumulated for this row yet
+            const float alpha = (!grow || fresh) ? (grow ? 0.0f : 1.0f) : ex2_approx(m_run - m_new);
             const float m_sub = (m_new == -INFINITY) ? 0.0f : m_new;
             float ps0 = 0.0f, ps1 = 0.0f;
             uint32_t packed[kP64Tok / 2];
@@ -224,7 +225,9 @@ paged_attn_prefill64_kernel(const __grid_constant__ CUtensorMap tmap_q, const __
             if (ti > 0) {   // P V of the previous tile must be complete before P is overwritten or O is rescaled
                 mbar_wait(o_full, (ti - 1) & 1);
                 tc_fence_after();
-                const bool rescale = grow && alpha != 0.0f;
+                // (alpha may underflow to exactly 0 when the maximum jumps by > 126 log2 units, e.g. under a steep ALiBi
+                // slope: the stale accumulation must then still be wiped, so "fresh" is tracked separately)
+                const bool rescale = grow && !fresh;
                 if (__any_sync(0xffffffffu, rescale)) {
                     const float f = rescale ? alpha : 1.0f;
 #pragma unroll

@@ -39,6 +39,7 @@ struct AttnArgs {
     float* ws_ml;       // [n_items][n_kv_heads][n_splits][R][2]
     float* ws_o;        // [n_items][n_kv_heads][n_splits][R][D]
     int consumer_warps; // 8 (one CTA per SM) or 4 (two CTAs per SM); host-side choice, see attn_pick_warps
+    const float* alibi; // [n_q_heads] ALiBi slopes (natural-log units) or nullptr: score += slope * (key pos - query pos)
 };
 
 template <int D, int W>
@@ -169,6 +170,10 @@ paged_attn_splitkv_kernel(const __grid_constant__ CUtensorMap tmap_kv, const Att
 #pragma unroll
             for (int i = 0; i < CH * 8; ++i) qreg[i] = q_s[hh * CH * 8 + i];
         }
+        // ALiBi slope of each row's head, in log2 units (0 without ALiBi: the fused multiply-add below is then a no-op)
+        float slope[R];
+#pragma unroll
+        for (int r = 0; r < R; ++r) slope[r] = a.alibi ? a.alibi[kvh * G + r % G] * 1.4426950408889634f : 0.0f;
         uint32_t stage = 0, phase = 0;
         for (int ti = t0; ti < t1; ++ti) {
             const uint8_t* ktile = stages + stage * attn_stage_bytes<D, W>();
@@ -212,7 +217,7 @@ paged_attn_splitkv_kernel(const __grid_constant__ CUtensorMap tmap_kv, const Att
                     float sc = part[r] + __shfl_xor_sync(0xffffffffu, part[r], 16);
                     const int q_pos = item.pos0 + r / G;
                     const bool ok = (j < n_mine) && (tok0 + rt <= q_pos) && (r < rows);
-                    sc = ok ? sc : -INFINITY;
+                    sc = ok ? fmaf(slope[r], static_cast<float>(tok0 + rt - q_pos), sc) : -INFINITY;
                     float mx = sc;
 #pragma unroll
                     for (int o = 8; o > 0; o >>= 1) mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, o));
@@ -381,7 +386,20 @@ static inline int attn_pick_warps(int64_t ctas) {
 
 }  // namespace hds
 
+// ALiBi slopes for the NEXT paged-attention launch of this thread (either kernel family); consumed by that launch.
+static thread_local const float* g_next_alibi = nullptr;
+const float* hds::attn_take_alibi() {
+    const float* p = g_next_alibi;
+    g_next_alibi = nullptr;
+    return p;
+}
+
 using namespace hds;
+
+extern "C" int hds_attention_next_alibi(const float* slopes) {
+    g_next_alibi = slopes;
+    return HDS_OK;
+}
 
 extern "C" int64_t hds_paged_attention_splitkv_workspace_bytes(int n_items, int n_q_heads, int n_kv_heads,
                                                                int head_dim, int max_splits, int rows_per_item) {
@@ -397,6 +415,7 @@ extern "C" int hds_paged_attention_splitkv(const void* q, void* out, const void*
                                                 int rows_per_item, int n_q_heads, int n_kv_heads, int head_dim,
                                                 int block_size, int n_splits, float scale, void* workspace,
                                                 int64_t workspace_bytes, int dtype, void* stream) {
+    const float* alibi = attn_take_alibi();
     HDS_REQUIRE(head_dim == 64 || head_dim == 128, "paged_attention_splitkv: head_dim must be 64 or 128");
     HDS_REQUIRE(block_size == 16 || block_size == 32 || block_size == 64 || block_size == 128,
                 "paged_attention_splitkv: block_size must be 16/32/64/128");
@@ -423,6 +442,7 @@ extern "C" int hds_paged_attention_splitkv(const void* q, void* out, const void*
     a.block_size = block_size;
     a.n_splits = n_splits;
     a.scale_log2 = scale * 1.4426950408889634f;
+    a.alibi = alibi;
     const int64_t units = static_cast<int64_t>(n_items) * n_kv_heads;
     char* ws = reinterpret_cast<char*>(workspace);
     a.counters = reinterpret_cast<int32_t*>(ws);

@@ -43,6 +43,7 @@ def _declare_cuda(lib: ctypes.CDLL) -> None:
         "hds_norm": [P, L, P, I, I, P, P, L, P, P, P, I, I, F, I, I, I, P],
         "hds_norm_tp": [I, I, I, P, L, P, P, I, P, P, P, L, P, P, I, I, I, P, P, I, F, I, I, P],
         "hds_fp8_next_weight_format": [I],
+        "hds_attention_next_alibi": [P],
         "hds_tp_ctx_create": [I, I, P],
         "hds_tp_ctx_destroy": [I],
         "hds_tp_arm": [I, I, I],

@@ -89,8 +89,10 @@ def gather_kv(kv_cache_layer: torch.Tensor, block_table_row: torch.Tensor, kv_le
 
 
 def paged_attention(q: torch.Tensor, kv_cache_layer: torch.Tensor, block_tables: torch.Tensor, items: torch.Tensor,
-                    n_q_heads: int, n_kv_heads: int, scale: float, out: Optional[torch.Tensor] = None) -> torch.Tensor:
-    """q: [T, n_q_heads, d]; items: int32 [n, 4] rows (seq, q_row0, n_q, pos0). Causal over absolute positions."""
+                    n_q_heads: int, n_kv_heads: int, scale: float, out: Optional[torch.Tensor] = None,
+                    alibi: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """q: [T, n_q_heads, d]; items: int32 [n, 4] rows (seq, q_row0, n_q, pos0). Causal over absolute positions.
+    ``alibi``: [n_q_heads] slopes, score += slope * (key position - query position)."""
     T, _, d = q.shape
     if out is None:
         out = torch.zeros_like(q)
@@ -104,6 +106,8 @@ def paged_attention(q: torch.Tensor, kv_cache_layer: torch.Tensor, block_tables:
         s = torch.einsum("qhd,khd->hqk", qq, k) * scale
         kv_pos = torch.arange(kv_len, device=q.device)[None, None, :]
         q_pos = (pos0 + torch.arange(n_q, device=q.device))[None, :, None]
+        if alibi is not None:
+            s = s + alibi.float().to(s.device)[:, None, None] * (kv_pos - q_pos).float()
         s = s.masked_fill(kv_pos > q_pos, float("-inf"))
         p = torch.softmax(s, dim=-1)
         out[q_row0:q_row0 + n_q] = torch.einsum("hqk,khd->qhd", p, v).to(out.dtype)
@@ -122,6 +126,16 @@ def embed(ids: torch.Tensor, weight: torch.Tensor, pos_weight: Optional[torch.Te
 
 def default_inv_freq(rotary_dim: int, theta: float = 10000.0, device=None) -> torch.Tensor:
     return 1.0 / (theta ** (torch.arange(0, rotary_dim, 2, dtype=torch.float32, device=device) / rotary_dim))
+
+
+def alibi_slopes(n_heads: int) -> torch.Tensor:
+    """ALiBi head slopes (Press et al.): a geometric sequence for the largest power of two <= n_heads, interleaved with
+    the odd terms of the next power's sequence for the remaining heads. fp32 [n_heads]."""
+    base = 2 ** math.floor(math.log2(n_heads))
+    first = [2.0 ** (-8.0 * (i + 1) / base) for i in range(base)]
+    if base < n_heads:
+        first += [2.0 ** (-4.0 * (2 * i + 1) / base) for i in range(n_heads - base)]
+    return torch.tensor(first, dtype=torch.float32)
 
 
 def attention_scale(head_dim: int) -> float:

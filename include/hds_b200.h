@@ -222,6 +222,11 @@ int hds_paged_attention_splitkv_static(const void* q, void* out, const void* kv_
                                        int n_kv_heads, int head_dim, int block_size, int n_splits, float scale,
                                        int dtype, void* stream);
 
+/* ALiBi (Bloom, Falcon-RW, MPT): slopes = device pointer to n_q_heads floats. The NEXT hds_paged_attention_splitkv /
+ * _prefill / _packed launch of the calling thread adds slope[head] * (key position - query position) to every score
+ * before the softmax, then the setting is cleared. (hds_paged_attention_splitkv_static ignores it.) */
+int hds_attention_next_alibi(const float* slopes);
+
 /* tcgen05 paged attention for items with up to 128 query tokens (prefill / chunked continuation): QK^T and
  * PV on the tensor cores with TMEM accumulators, TMA page gathers, online softmax in registers.
  * n_q_rows = total rows of q (bounds the Q tensor map). n_splits > 1 splits each item's KV range over several

@@ -300,6 +300,15 @@ def _hf_model(kind):
         return GPTNeoXForCausalLM(GPTNeoXConfig(vocab_size=2048, hidden_size=512, num_hidden_layers=3, num_attention_heads=4,
                                                 intermediate_size=2048, rotary_pct=0.25, max_position_embeddings=1024,
                                                 hidden_dropout=0.0, attention_dropout=0.0)).eval()
+    if kind == "bloom":
+        from transformers import BloomConfig, BloomForCausalLM
+        return BloomForCausalLM(BloomConfig(vocab_size=2048, hidden_size=768, n_layer=3, n_head=6, hidden_dropout=0.0,
+                                            attention_dropout=0.0)).eval()
+    if kind == "falcon_alibi":
+        from transformers import FalconConfig, FalconForCausalLM
+        return FalconForCausalLM(FalconConfig(vocab_size=2048, hidden_size=512, num_hidden_layers=3, num_attention_heads=4,
+                                              multi_query=False, parallel_attn=False, new_decoder_architecture=False, alibi=True,
+                                              bias=True, hidden_dropout=0.0, attention_dropout=0.0)).eval()
     from transformers import LlamaConfig, LlamaForCausalLM
     cfg = LlamaConfig(vocab_size=2048, hidden_size=512, intermediate_size=1408, num_hidden_layers=3, num_attention_heads=4,
                       num_key_value_heads=2, max_position_embeddings=1024)
@@ -307,7 +316,7 @@ def _hf_model(kind):
 
 
 # gpt2 / gptj / gpt_neox: the families the reference serves through its v1 transformer_inference op only
-@pytest.mark.parametrize("kind", ["opt", "llama", "gpt2", "gptj", "gpt_neox"])
+@pytest.mark.parametrize("kind", ["opt", "llama", "gpt2", "gptj", "gpt_neox", "bloom", "falcon_alibi"])
 def test_v1_init_inference_kernel_inject_gpu(kind):
     """``init_inference(replace_with_kernel_inject=True)`` on the GPU (v1 API): the injected engine runs the sm_100a
     kernels, its logits track the HuggingFace model's fp32 logits for a prompt and for a continuation over the live KV

@@ -416,6 +416,64 @@ def test_attention_packed_gqa_decode(dtype, n_q_heads, n_kv, bs):
         assert int(ws[:len(items) * n_kv * 32].view(torch.int32).abs().max()) == 0
 
 
+@pytest.mark.parametrize("dtype", DTYPES)
+def test_attention_alibi_all_kernels(dtype):
+    """ALiBi (``hds_attention_next_alibi``): score += slope[head] * (key - query position) in the split-KV decode kernel
+    (1 and several rows per item, split and unsplit), the tensor-core prefill kernel (unsplit / split-KV) and the
+    head-packed GQA kernel, against the fp32 oracle; the setting is consumed by ONE launch (the next one is plain)."""
+    scale_of = lambda d: 1.0 / math.sqrt(d)
+    # split-KV decode, MHA (Bloom-like: 6 heads = interleaved slope sequence) and GQA rows
+    for n_q_heads, n_kv, d, bs, rows in ((6, 6, 64, 128, 1), (8, 8, 128, 64, 1), (16, 4, 128, 64, 1), (4, 4, 128, 64, 8)):
+        specs = [(0, rows), (5, rows), (127, 1), (1000, rows), (4095, 1), (333, 1)]
+        q, cache, tables, items = build_paged_problem(specs, n_q_heads, n_kv, d, bs, dtype, seed=11)
+        items_t = torch.tensor(items, dtype=torch.int32, device="cuda")
+        slopes = ref.alibi_slopes(n_q_heads).cuda()
+        G = n_q_heads // n_kv
+        R = rows * G
+        want = ref.paged_attention(q, cache, tables, items_t.cpu(), n_q_heads, n_kv, scale_of(d), alibi=slopes)
+        plain = ref.paged_attention(q, cache, tables, items_t.cpu(), n_q_heads, n_kv, scale_of(d))
+        assert (want.float() - plain.float()).abs().max() > 0.05          # the bias matters in this problem
+        for n_splits in (1, 3):
+            ws = torch.zeros(max(K().splitkv_workspace_bytes(len(items), n_q_heads, n_kv, d, n_splits, R), 16), dtype=torch.uint8,
+                             device="cuda")
+            out = torch.zeros_like(q)
+            K().paged_attention_splitkv(q, out, cache, tables, items_t, len(items), R, n_q_heads, n_kv, d, bs, n_splits,
+                                        scale_of(d), ws, alibi=slopes)
+            torch.testing.assert_close(out.float(), want.float(), **tol(dtype))
+            out.zero_()
+            K().paged_attention_splitkv(q, out, cache, tables, items_t, len(items), R, n_q_heads, n_kv, d, bs, n_splits,
+                                        scale_of(d), ws)
+            torch.testing.assert_close(out.float(), plain.float(), **tol(dtype))
+    # tensor-core prefill
+    # (32 heads: the steepest slope moves the row maximum by > 126 log2 units from one key tile to the next, so the rescale
+    # factor of the accumulator underflows to exactly 0 — stale contributions must still be wiped)
+    for n_q_heads, n_kv, d, bs in ((4, 4, 128, 64), (6, 6, 64, 128), (8, 2, 128, 16), (32, 8, 128, 64)):
+        specs = [(0, 128), (0, 17), (100, 64), (1000, 128), (4000, 96), (63, 1)]
+        q, cache, tables, items = build_paged_problem(specs, n_q_heads, n_kv, d, bs, dtype, seed=12)
+        items_t = torch.tensor(items, dtype=torch.int32, device="cuda")
+        slopes = ref.alibi_slopes(n_q_heads).cuda()
+        want = ref.paged_attention(q, cache, tables, items_t.cpu(), n_q_heads, n_kv, scale_of(d), alibi=slopes)
+        out = torch.zeros_like(q)
+        K().paged_attention_prefill(q, out, cache, tables, items_t, len(items), n_q_heads, n_kv, d, bs, scale_of(d), alibi=slopes)
+        torch.testing.assert_close(out.float(), want.float(), **tol(dtype))
+        ws = torch.zeros(K().prefill_workspace_bytes(len(items), n_q_heads, d, 3), dtype=torch.uint8, device="cuda")
+        out.zero_()
+        K().paged_attention_prefill(q, out, cache, tables, items_t, len(items), n_q_heads, n_kv, d, bs, scale_of(d), n_splits=3,
+                                    workspace=ws, alibi=slopes)
+        torch.testing.assert_close(out.float(), want.float(), **tol(dtype))
+    # head-packed grouped-query decode: every row of the tile has its own head's slope
+    n_q_heads, n_kv, d, bs = 32, 4, 128, 64
+    specs = [(0, 1), (100, 1), (1000, 1), (4000, 1), (5, 3), (700, 6)]
+    q, cache, tables, items = build_paged_problem(specs, n_q_heads, n_kv, d, bs, dtype, seed=13)
+    items_t = torch.tensor(items, dtype=torch.int32, device="cuda")
+    slopes = ref.alibi_slopes(n_q_heads).cuda()
+    want = ref.paged_attention(q, cache, tables, items_t.cpu(), n_q_heads, n_kv, scale_of(d), alibi=slopes)
+    out = torch.zeros_like(q)
+    K().paged_attention_prefill(q, out, cache, tables, items_t, len(items), n_q_heads, n_kv, d, bs, scale_of(d), packed=True,
+                                alibi=slopes)
+    torch.testing.assert_close(out.float(), want.float(), **tol(dtype))
+
+
 def test_attention_prefill_64_key_tiles_subprocess():
     """The opt-in 64-key-tile / two-CTAs-per-SM shape of the tensor-core attention kernel (HDS_PREFILL_TILE=64, read once per
     process): the prefill attention tests of this file are re-run in a child process with the variable set."""

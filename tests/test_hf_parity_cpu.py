@@ -54,11 +54,20 @@ def _tiny(family):
         return T.GPTNeoXForCausalLM(T.GPTNeoXConfig(intermediate_size=256, rotary_pct=0.5, use_parallel_residual=True, **common))
     if family == "gpt_neox_sequential":
         return T.GPTNeoXForCausalLM(T.GPTNeoXConfig(intermediate_size=256, rotary_pct=1.0, use_parallel_residual=False, **common))
+    if family == "bloom":
+        return T.BloomForCausalLM(T.BloomConfig(hidden_size=128, n_layer=2, n_head=4, vocab_size=300))
+    if family == "bloom_6heads":      # a head count that is not a power of two: the interleaved slope sequence
+        return T.BloomForCausalLM(T.BloomConfig(hidden_size=192, n_layer=2, n_head=6, vocab_size=300))
+    if family == "falcon_alibi":
+        return T.FalconForCausalLM(T.FalconConfig(hidden_size=128, num_hidden_layers=2, num_attention_heads=4, vocab_size=300,
+                                                  multi_query=False, parallel_attn=False, new_decoder_architecture=False,
+                                                  alibi=True, bias=True))
     raise KeyError(family)
 
 
 FAMILIES = ["llama", "llama_mha_bias", "mistral", "qwen2", "opt", "falcon_mqa", "falcon_new", "phi", "phi3", "mixtral", "qwen2_moe",
-            "gpt2", "gptj", "gpt_neox", "gpt_neox_sequential"]
+            "gpt2", "gptj", "gpt_neox", "gpt_neox_sequential",
+            "bloom", "bloom_6heads", "falcon_alibi"]
 
 
 @pytest.mark.parametrize("family", FAMILIES)

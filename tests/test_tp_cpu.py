@@ -65,6 +65,11 @@ CASES = {
                           vocab=101, norm="layer", act="relu", gated_mlp=False, pos_emb="learned", learned_pos_offset=2,
                           max_positions=256, qkv_bias=True, attn_out_bias=True, mlp_bias=True, norm_bias=True,
                           tie_word_embeddings=True), 2),
+    # ALiBi: each rank adds the slopes of ITS heads; 6 heads = the interleaved (non power of two) slope sequence
+    "bloom_alibi_tp3": (dict(model_type="bloom", n_layers=2, hidden=96, n_heads=6, n_kv_heads=6, head_dim=16, intermediate=384,
+                             vocab=101, norm="layer", act="gelu_tanh", gated_mlp=False, pos_emb="alibi", embed_norm=True,
+                             max_positions=256, qkv_bias=True, attn_out_bias=True, mlp_bias=True, norm_bias=True,
+                             tie_word_embeddings=True), 3),
 }
 
 

@@ -17,7 +17,7 @@ def shard_full_weights(spec, full: ModelWeights, rank: int, world: int) -> Model
     vr = _rows(info.kv_heads, d, (nq + nkv) * d)
     a, b = info.inter_range
     out = ModelWeights(embed=full.embed, pos_embed=full.pos_embed, final_norm_g=full.final_norm_g,
-                       final_norm_b=full.final_norm_b)
+                       final_norm_b=full.final_norm_b, embed_norm_g=full.embed_norm_g, embed_norm_b=full.embed_norm_b)
     va, vb = info.vocab_range
     out.lm_head = full.lm_head[va:vb].contiguous()
     out.lm_head_b = full.lm_head_b[va:vb].contiguous() if full.lm_head_b is not None else None
