@@ -70,6 +70,8 @@ def map_llama_like(name: str, t: torch.Tensor, spec: ArchSpec) -> List[Piece]:
         return []
     parts = rest.split(".")
     kind = parts[-1]
+    if kind.startswith("lora_"):
+        return []   # adapter tensors of LoRA-wrapped projections (folded into the base weight by the hybrid engine)
     if rest.startswith("input_layernorm."):
         return [(layer, "norm1.g", t)]
     if rest.startswith("post_attention_layernorm."):
@@ -130,6 +132,8 @@ def map_opt(name: str, t: torch.Tensor, spec: ArchSpec) -> List[Piece]:
         if "decoder.final_layer_norm." in name:
             return [(None, "final_norm.g" if kind == "weight" else "final_norm.b", t)]
         return []  # lm_head is tied
+    if name.split(".")[-1].startswith("lora_"):
+        return []
     parts = rest.split(".")
     if parts[0] == "self_attn":
         proj = parts[1]
@@ -175,6 +179,8 @@ def map_falcon(name: str, t: torch.Tensor, spec: ArchSpec) -> List[Piece]:
         if ".ln_f." in name or name.startswith("ln_f."):
             return [(None, "final_norm.g" if kind == "weight" else "final_norm.b", t)]
         return []
+    if name.split(".")[-1].startswith("lora_"):
+        return []
     parts = rest.split(".")
     gb = "g" if kind == "weight" else "b"
     if parts[0] == "self_attention":
@@ -211,6 +217,8 @@ def map_phi(name: str, t: torch.Tensor, spec: ArchSpec) -> List[Piece]:
         if name == "lm_head.bias":
             return [(None, "lm_head_b", t)]
         return []
+    if name.split(".")[-1].startswith("lora_"):
+        return []
     parts = rest.split(".")
     if parts[0] == "self_attn":
         if parts[1] in ("q_proj", "k_proj", "v_proj"):
@@ -239,6 +247,8 @@ def map_qwen(name: str, t: torch.Tensor, spec: ArchSpec) -> List[Piece]:
             return [(None, "final_norm.g", t)]
         if name == "lm_head.weight":
             return [(None, "lm_head", t)]
+        return []
+    if name.split(".")[-1].startswith("lora_"):
         return []
     parts = rest.split(".")
     if parts[0] == "ln_1":

@@ -359,3 +359,82 @@ def test_zero3_frozen_params_checkpoint_and_init_broadcast_2ranks(tmp_path):
     shards = res[0]["fp32_from_shards"]
     for k, v in res[0]["trained"].items():
         torch.testing.assert_close(shards[k], v, rtol=1e-6, atol=1e-7)
+
+
+class _ChatLoRALinear(torch.nn.Module):
+    """DeepSpeed-Chat's LinearLayer_LoRA layout: frozen base weight + right [in, r] / left [r, out] adapters."""
+
+    def __init__(self, base: torch.nn.Linear, r=4, scaling=2.0):
+        super().__init__()
+        self.weight = base.weight
+        self.weight.requires_grad = False
+        self.bias = base.bias
+        self.lora_right_weight = torch.nn.Parameter(torch.randn(base.in_features, r) * 0.05)
+        self.lora_left_weight = torch.nn.Parameter(torch.randn(r, base.out_features) * 0.05)
+        self.lora_scaling = scaling / r
+
+    def forward(self, x):
+        return torch.nn.functional.linear(x, self.weight, self.bias) + (x @ self.lora_right_weight @ self.lora_left_weight) * self.lora_scaling
+
+
+@pytest.mark.parametrize("stage", [0, 3])
+def test_hybrid_engine_lora_generate_tracks_training(stage):
+    """RLHF loop on one rank: generate -> train the LoRA adapters -> generate again. The injected inference copy must see
+    the fused adapters of the CURRENT step (ref: runtime/hybrid_engine.py:132-168), the training weights stay un-fused,
+    ZeRO-3 parameters are gathered for the refresh only."""
+    transformers = pytest.importorskip("transformers")
+    import hcache_deepspeed_b200 as ds
+    from hcache_deepspeed_b200.runtime.hybrid_engine import DeepSpeedHybridEngine
+    torch.manual_seed(0)
+    cfg = transformers.LlamaConfig(hidden_size=64, intermediate_size=128, num_hidden_layers=2, num_attention_heads=4,
+                                   num_key_value_heads=2, vocab_size=97, max_position_embeddings=256)
+    model = transformers.LlamaForCausalLM(cfg).float()
+    for layer in model.model.layers:
+        layer.self_attn.q_proj = _ChatLoRALinear(layer.self_attn.q_proj)
+        layer.mlp.down_proj = _ChatLoRALinear(layer.mlp.down_proj)
+    ds_cfg = {"train_micro_batch_size_per_gpu": 2, "optimizer": {"type": "AdamW", "params": {"lr": 5e-2}},
+              "zero_optimization": {"stage": stage, "stage3_param_persistence_threshold": 0},
+              "hybrid_engine": {"enabled": True, "max_out_tokens": 32}, "steps_per_print": 1000}
+    engine, _, _, _ = ds.initialize(model=model, config=ds_cfg, model_parameters=[p for p in model.parameters() if p.requires_grad])
+    assert isinstance(engine, DeepSpeedHybridEngine) and len(engine._lora_layers) == 4
+    prompt = torch.randint(1, 97, (2, 7))
+
+    def reference_generate():
+        """Greedy decoding with the training module itself (its forward applies the adapters un-fused)."""
+        ctx = engine._gather_context()
+        with ctx, torch.no_grad():
+            ids = prompt.clone()
+            for _ in range(6):
+                nxt = engine.module(ids).logits[:, -1].argmax(-1, keepdim=True)
+                ids = torch.cat([ids, nxt], dim=1)
+        return ids
+
+    engine.eval()
+    out0 = engine.generate(prompt, max_new_tokens=6, do_sample=False)
+    assert engine._inference_engine.injected and torch.equal(out0[:, :prompt.shape[1]], prompt)
+    assert torch.equal(out0, reference_generate())
+    first_engine = engine._inference_engine
+    engine.generate(prompt, max_new_tokens=2, do_sample=False)
+    assert engine._inference_engine is first_engine                 # nothing moved: no refresh
+    base_before = [m.weight.detach().clone() for m, _ in engine._lora_layers] if stage == 0 else None
+
+    engine.train()
+    for _ in range(3):
+        ids = torch.randint(1, 97, (2, 12))
+        loss = engine(input_ids=ids, labels=ids).loss
+        engine.backward(loss)
+        engine.step()
+    engine.eval()
+    out1 = engine.generate(prompt, max_new_tokens=6, do_sample=False)
+    assert engine._inference_engine is not first_engine             # the step counter moved: weights refreshed
+    assert torch.equal(out1, reference_generate())
+    assert not engine.is_lora_fused
+    if stage == 0:
+        for (m, _), w in zip(engine._lora_layers, base_before):
+            torch.testing.assert_close(m.weight.detach(), w, rtol=0, atol=1e-6)       # base weights came back un-fused
+    stats = engine.latency_stats()
+    assert stats["generate_s"] > 0 and stats["iterations"] >= 1
+    engine.release_inference_engine()
+    assert engine._inference_engine is None
+    engine.retake_inference_cache()
+    assert engine._inference_engine is not None
