@@ -18,6 +18,7 @@ import torch
 from ....ops import native
 from ....ops.host_bindings import SeqIn
 from ....utils.memory import pinned_zeros
+from . import fast_host_buffer
 from .manager_configs import DSStateManagerConfig
 from .sequence_descriptor import DSSequenceDescriptor
 
@@ -62,7 +63,12 @@ class RaggedBatchWrapper:
                         ("large", 4 * self._I), ("tables", S * self._stride)):
             self._off[name] = (off, n)
             off += n
-        self._host = pinned_zeros((off, ), torch.int32)
+        mode = fast_host_buffer.staging_mode() if self._device.type == "cuda" else None
+        if mode is not None:    # opt-in: natively allocated mapped (+ write-combined) staging memory
+            self._fast = fast_host_buffer.FastHostBuffer(off, torch.int32, mapped=True, write_combined=(mode == "wc"))
+            self._host = self._fast.tensor
+        else:
+            self._host = pinned_zeros((off, ), torch.int32)
         self._host_np = self._host.numpy()   # same memory: scalar / slice writes without tensor-op dispatch overhead
         self._dev = self._host if self._device.type == "cpu" else torch.zeros(off, dtype=torch.int32,
                                                                                device=self._device)

@@ -24,7 +24,8 @@ InferenceCoreBuilder = _mk("inference_core_ops", "cuda", ["hds_gemm", "hds_gemm_
 RaggedOpsBuilder = _mk("ragged_device_ops", "cuda", ["hds_paged_attention_splitkv", "hds_paged_attention_prefill", "hds_embed",
                                                        "hds_rope_kv_append", "hds_gather_rows", "hds_moe_topk_gating",
                                                        "hds_moe_scatter", "hds_moe_gather"],
-                       sources=("attention_splitkv.cu", "attention_prefill.cu", "elementwise.cu", "moe.cu"), depends=_TP)
+                       sources=("attention_splitkv.cu", "attention_prefill.cu", "elementwise.cu", "moe.cu", "host_buffer.cu"),
+                       depends=_TP)
 InferenceCutlassBuilder = _mk("cutlass_ops", "cuda", ["hds_moe_gemm"], sources=("moe.cu", ))
 RaggedUtilsBuilder = _mk("ragged_ops", "host", ["hds_alloc_create", "hds_build_batch"], sources=("host_runtime.cpp", ))
 InferenceBuilder = _mk("transformer_inference", "cuda", ["hds_gemm", "hds_norm", "hds_rope_kv_append"],

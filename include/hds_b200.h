@@ -222,6 +222,13 @@ int hds_paged_attention_splitkv_static(const void* q, void* out, const void* kv_
                                        int n_kv_heads, int head_dim, int block_size, int n_splits, float scale,
                                        int dtype, void* stream);
 
+/* Host staging buffers with explicit flags (ref: ragged/csrc/fast_host_buffer.cu). Always portable pinned memory;
+ * `mapped`: also addressable by the GPU (hds_host_buffer_device_ptr), `write_combined`: host stores bypass the CPU
+ * caches (fast to write and to DMA from, slow for the host to read back). */
+int hds_host_buffer_alloc(int64_t bytes, int mapped, int write_combined, void** out);
+int hds_host_buffer_device_ptr(void* host_ptr, void** out);
+int hds_host_buffer_free(void* host_ptr);
+
 /* ALiBi (Bloom, Falcon-RW, MPT): slopes = device pointer to n_q_heads floats. The NEXT hds_paged_attention_splitkv /
  * _prefill / _packed launch of the calling thread adds slope[head] * (key position - query position) to every score
  * before the softmax, then the setting is cleared. (hds_paged_attention_splitkv_static ignores it.) */

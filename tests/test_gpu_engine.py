@@ -350,3 +350,39 @@ def test_v1_init_inference_kernel_inject_gpu(kind):
     eng.restore_hidden_states(7, ctx, lat)
     restored = eng(input_ids=turn.cuda(), session_ids=[7]).logits.float().cpu()
     torch.testing.assert_close(restored, live, rtol=3e-2, atol=3e-2)
+
+
+@pytest.mark.parametrize("mode", ["mapped", "wc"])
+def test_fast_host_buffer_staging(mode, monkeypatch):
+    """Natively allocated staging memory (``hds_host_buffer_alloc``: pinned + mapped (+ write-combined), ref
+    ragged/csrc/fast_host_buffer.cu): the tensor view counts as pinned for torch, async copies out of it work, it has a
+    device-side address, and an engine whose ragged batch stages through it produces bit-identical logits."""
+    from hcache_deepspeed_b200.inference.v2 import build_engine_from_arch
+    from hcache_deepspeed_b200.inference.v2.ragged.fast_host_buffer import FastHostBuffer, allocate_fast_host_buffer
+    from hcache_deepspeed_b200.models.arch import named_arch
+    torch.zeros(1, device="cuda")        # torch answers is_pinned() with False until it has initialised CUDA itself
+    buf = FastHostBuffer(4096, torch.int32, mapped=True, write_combined=(mode == "wc"))
+    assert buf.tensor.is_pinned() and buf.device_ptr()
+    buf.tensor.numpy()[:] = torch.arange(4096, dtype=torch.int32).numpy()
+    dev = torch.empty(4096, dtype=torch.int32, device="cuda")
+    dev.copy_(buf.tensor, non_blocking=True)
+    torch.cuda.synchronize()
+    assert torch.equal(dev.cpu(), torch.arange(4096, dtype=torch.int32))
+    buf.free()
+    like = allocate_fast_host_buffer(torch.empty(3, 5, dtype=torch.float32))
+    assert like.shape == (3, 5) and like.is_pinned()
+
+    spec = named_arch("tiny-llama-test")
+    g = torch.Generator().manual_seed(2)
+    a, b = torch.randint(0, spec.vocab, (150, ), generator=g), torch.randint(0, spec.vocab, (9, ), generator=g)
+    nxt = torch.randint(0, spec.vocab, (2, ), generator=g)
+    plain = build_engine_from_arch(spec, _cfg(), seed=5, dtype=torch.bfloat16, device=torch.device("cuda"))
+    want, _ = plain.put([1, 2], [a, b])
+    want2, _ = plain.put([1, 2], [nxt[0:1], nxt[1:2]])
+    monkeypatch.setenv("HDS_FAST_HOST_BUFFER", mode)
+    eng = build_engine_from_arch(spec, _cfg(), seed=5, dtype=torch.bfloat16, device=torch.device("cuda"))
+    assert getattr(eng._batch, "_fast", None) is not None
+    got, _ = eng.put([1, 2], [a, b])
+    got2, _ = eng.put([1, 2], [nxt[0:1], nxt[1:2]])
+    torch.testing.assert_close(got.float(), want.float(), rtol=0, atol=0)
+    torch.testing.assert_close(got2.float(), want2.float(), rtol=0, atol=0)
