@@ -159,12 +159,16 @@ class GPTNeoXPolicy(InferenceV2Policy):
     pass
 
 
+class GPTNeoPolicy(InferenceV2Policy):
+    """Alternating global / sliding-window layers (``hds_attention_next_window``), unscaled scores."""
+
+
 class BloomPolicy(InferenceV2Policy):
     """ALiBi attention (``hds_attention_next_alibi``) + LayerNorm on the embeddings."""
 
 
 MODEL_TYPE_TO_POLICY = {
-    "gpt2": GPT2Policy, "gptj": GPTJPolicy, "gpt_neox": GPTNeoXPolicy, "bloom": BloomPolicy,
+    "gpt2": GPT2Policy, "gptj": GPTJPolicy, "gpt_neox": GPTNeoXPolicy, "bloom": BloomPolicy, "gpt_neo": GPTNeoPolicy,
     "llama": Llama2Policy, "opt": OPTPolicy, "mistral": MistralPolicy, "mixtral": MixtralPolicy, "falcon": FalconPolicy,
     "phi": PhiPolicy, "phi3": Phi3Policy, "qwen": QwenPolicy, "qwen2": Qwen2Policy, "qwen2_moe": Qwen2MoePolicy,
     "internlm": Llama2Policy,

@@ -33,6 +33,8 @@ class ArchSpec:
     pos_emb: str = "rope"  # "rope" | "learned" | "alibi" | "none"
     alibi_scale: float = 1.0  # multiplies the ALiBi slopes (Falcon adds the bias BEFORE its 1/sqrt(d): scale = 1/sqrt(d))
     embed_norm: bool = False  # LayerNorm on the token embeddings (Bloom's word_embeddings_layernorm)
+    sliding_window: int = 0  # > 0: a query at position p attends to the keys (p - window, p] (Mistral, Phi-3)
+    layer_windows: Optional[List[int]] = None  # per-layer override of sliding_window (GPT-Neo: global / local alternate)
     rope_theta: float = 10000.0
     rotary_dim: Optional[int] = None  # None = head_dim
     rope_scaling: Optional[Dict[str, Any]] = None
@@ -82,6 +84,9 @@ class ArchSpec:
     def kv_bytes_per_token_layer(self, elem: int = 2) -> int:
         """Bytes plain KV offload stores per token per layer."""
         return 2 * self.kv_dim * elem
+
+    def window_of(self, layer: int) -> int:
+        return int(self.layer_windows[layer]) if self.layer_windows is not None else int(self.sliding_window)
 
     def scaled(self, **kw) -> "ArchSpec":
         return replace(self, **kw)
@@ -146,6 +151,28 @@ def _rope_theta(cfg, default=10000.0) -> float:
     return float(theta if theta is not None else default)
 
 
+def _window_fields(cfg, mt) -> Dict[str, Any]:
+    """Sliding-window settings of the llama-like families. Mistral / Phi-3: ``sliding_window`` on every layer. Qwen2:
+    only with ``use_sliding_window``, and then on the layers HF marks ``sliding_attention`` (``layer_types``) or, for
+    older configs, on layers >= ``max_window_layers``."""
+    w = _get(cfg, "sliding_window")
+    if not w or mt not in ("mistral", "phi3", "qwen2", "mixtral", "qwen2_moe"):
+        return {}
+    n = _get(cfg, "num_hidden_layers")
+    if mt in ("qwen2", "qwen2_moe"):
+        if not _get(cfg, "use_sliding_window", default=False):
+            return {}
+        types = _get(cfg, "layer_types")
+        if types:
+            return {"layer_windows": [int(w) if t == "sliding_attention" else 0 for t in types]}
+        first = _get(cfg, "max_window_layers", default=n)
+        return {"layer_windows": [int(w) if i >= first else 0 for i in range(n)]}
+    types = _get(cfg, "layer_types")
+    if types and any(t != "sliding_attention" for t in types):
+        return {"layer_windows": [int(w) if t == "sliding_attention" else 0 for t in types]}
+    return {"sliding_window": int(w)}
+
+
 @register_arch("llama", "mistral", "qwen2", "phi3", "internlm")
 def _llama_like(cfg) -> ArchSpec:
     mt = _get(cfg, "model_type")
@@ -160,7 +187,7 @@ def _llama_like(cfg) -> ArchSpec:
         qkv_bias=(mt == "qwen2") or bool(_get(cfg, "attention_bias", default=False)),
         attn_out_bias=bool(_get(cfg, "attention_bias", default=False)) and mt != "qwen2",
         mlp_bias=bool(_get(cfg, "mlp_bias", default=False)),
-        tie_word_embeddings=bool(_get(cfg, "tie_word_embeddings", default=False)))
+        tie_word_embeddings=bool(_get(cfg, "tie_word_embeddings", default=False)), **_window_fields(cfg, mt))
 
 
 @register_arch("opt")
@@ -243,6 +270,24 @@ def _gpt2(cfg) -> ArchSpec:
         norm_eps=_get(cfg, "layer_norm_epsilon", default=1e-5), act=_get(cfg, "activation_function", default="gelu_new"),
         gated_mlp=False, pos_emb="learned", learned_pos_offset=0, max_positions=_get(cfg, "n_positions", default=1024),
         qkv_bias=True, attn_out_bias=True, mlp_bias=True, norm_bias=True, tie_word_embeddings=True)
+
+
+@register_arch("gpt_neo")
+def _gpt_neo(cfg) -> ArchSpec:
+    """GPT-Neo: learned positions, UNSCALED attention scores, layers alternate between global and local (sliding-window)
+    attention as listed in ``attention_layers``."""
+    h = _get(cfg, "hidden_size")
+    nh = _get(cfg, "num_heads", "num_attention_heads")
+    n = _get(cfg, "num_layers", "num_hidden_layers")
+    kinds = list(_get(cfg, "attention_layers", default=["global"] * n))
+    win = int(_get(cfg, "window_size", default=256))
+    return ArchSpec(
+        model_type="gpt_neo", n_layers=n, hidden=h, n_heads=nh, n_kv_heads=nh, head_dim=h // nh,
+        intermediate=_get(cfg, "intermediate_size", default=None) or 4 * h, vocab=_get(cfg, "vocab_size"), norm="layer",
+        norm_eps=_get(cfg, "layer_norm_epsilon", default=1e-5), act=_get(cfg, "activation_function", default="gelu_new"),
+        gated_mlp=False, pos_emb="learned", learned_pos_offset=0, max_positions=_get(cfg, "max_position_embeddings", default=2048),
+        qkv_bias=False, attn_out_bias=True, mlp_bias=True, norm_bias=True, tie_word_embeddings=True, attn_scale=1.0,
+        layer_windows=[win if k == "local" else 0 for k in kinds])
 
 
 @register_arch("gptj")

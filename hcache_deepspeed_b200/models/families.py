@@ -431,3 +431,39 @@ def map_bloom(name: str, t: torch.Tensor, spec: ArchSpec) -> List[Piece]:
         if parts[1] == "dense_4h_to_h":
             return [(layer, f"mlp.down{sfx}", t)]
     return []
+
+
+# ---------------------------------------------------------------------------------------------------
+@register_mapper("gpt_neo")
+def map_gpt_neo(name: str, t: torch.Tensor, spec: ArchSpec) -> List[Piece]:
+    """GPT-Neo (ref: module_inject/containers/gptneo.py): nn.Linear projections under ``attn.attention``, no Q/K/V bias."""
+    layer, rest = _split_layer(name)
+    kind = name.split(".")[-1]
+    if kind not in ("weight", "bias"):
+        return []
+    gb = "g" if kind == "weight" else "b"
+    if layer is None:
+        if name.endswith("wte.weight"):
+            return [(None, "embed", t)]
+        if name.endswith("wpe.weight"):
+            return [(None, "pos_embed", t)]
+        if "ln_f." in name:
+            return [(None, f"final_norm.{gb}", t)]
+        return []
+    parts = rest.split(".")
+    sfx = _wb(kind)
+    if parts[0] == "ln_1":
+        return [(layer, f"norm1.{gb}", t)]
+    if parts[0] == "ln_2":
+        return [(layer, f"norm2.{gb}", t)]
+    if parts[0] == "attn" and len(parts) == 4 and parts[1] == "attention":
+        if parts[2] in ("q_proj", "k_proj", "v_proj"):
+            return [(layer, f"attn.{parts[2][0]}{sfx}", t)]
+        if parts[2] == "out_proj":
+            return [(layer, f"attn.o{sfx}", t)]
+    if parts[0] == "mlp" and len(parts) == 3:
+        if parts[1] == "c_fc":
+            return [(layer, f"mlp.up{sfx}", t)]
+        if parts[1] == "c_proj":
+            return [(layer, f"mlp.down{sfx}", t)]
+    return []

@@ -506,7 +506,7 @@ class RaggedTransformer:
                                    comm=self.comm, tp_wait=self._take_tp_wait())
             attn = self.attn_buf[:T]
             ops.attention(self.q_buf[:T], attn, kv_layer, batch, self.n_q, self.n_kv, self.d, self.scale,
-                          ws_small=self.ws_small, ws_large=self.ws_large, alibi=self.alibi)
+                          ws_small=self.ws_small, ws_large=self.ws_large, alibi=self.alibi, window=s.window_of(li))
             if s.parallel_residual:
                 xm = xn
                 if two_norms:

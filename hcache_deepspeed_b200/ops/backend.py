@@ -81,12 +81,13 @@ class CpuOps:
             k = ref.rope_rotate_half(k, tok_pos, inv_freq, rot_dim)
         ref.kv_append(kv_layer, k, v, tok_slot)
 
-    def attention(self, q, out, kv_layer, batch, n_q, n_kv, d, scale, ws_small=None, ws_large=None, alibi=None):
+    def attention(self, q, out, kv_layer, batch, n_q, n_kv, d, scale, ws_small=None, ws_large=None, alibi=None, window=0):
         T = q.shape[0]
         q3, o3 = q.view(T, n_q, d), out.view(T, n_q, d)
         for items in (batch.items_small(), batch.items_large()):
             if items.shape[0]:
-                ref.paged_attention(q3, kv_layer, batch.block_tables(), items, n_q, n_kv, scale, out=o3, alibi=alibi)
+                ref.paged_attention(q3, kv_layer, batch.block_tables(), items, n_q, n_kv, scale, out=o3, alibi=alibi,
+                                    window=window)
 
     # ---- misc ---------------------------------------------------------------------------------------
     def embed(self, ids, weight, out, pos_weight=None, tok_pos=None, pos_offset=0):
@@ -215,26 +216,30 @@ class CudaOps:
             self.k.gemm(latents, w_kv, bias=b_kv, out=scratch)
             self.k.rope_kv_append(scratch, scratch, kv_layer, tok_pos, tok_slot, inv_freq, 0, n_kv, d, rot_dim, block_size)
 
-    def attention(self, q, out, kv_layer, batch, n_q, n_kv, d, scale, ws_small=None, ws_large=None, alibi=None):
+    def attention(self, q, out, kv_layer, batch, n_q, n_kv, d, scale, ws_small=None, ws_large=None, alibi=None, window=0):
         k = self.k
         bs = batch.block_size
+        # with a sliding window an item reads at most window + one tile of keys: size the KV split for that
+        seen = (lambda n_kv_tokens: min(n_kv_tokens, window + 256)) if window else (lambda n_kv_tokens: n_kv_tokens)
         if batch.n_items_small:
             n = batch.n_items_small
             if use_packed_decode(n_q, n_kv, d):
                 # grouped-query decode: the group's query heads share one pass over the KV pages, on the tensor cores
-                splits = pick_packed_splits(n, n_kv, batch.max_kv_len_small)
+                splits = pick_packed_splits(n, n_kv, seen(batch.max_kv_len_small))
                 k.paged_attention_prefill(q, out, kv_layer, batch.block_tables(), batch.items_small(), n, n_q, n_kv, d, bs,
                                           scale, n_splits=splits, workspace=ws_large if splits > 1 else None, packed=True,
-                                          alibi=alibi)
+                                          alibi=alibi, window=window)
             else:
-                splits = pick_decode_splits(n, n_kv, batch.max_kv_len_small)
+                splits = pick_decode_splits(n, n_kv, seen(batch.max_kv_len_small))
                 k.paged_attention_splitkv(q, out, kv_layer, batch.block_tables(), batch.items_small(), n,
-                                          batch.rows_per_small_item, n_q, n_kv, d, bs, splits, scale, ws_small, alibi=alibi)
+                                          batch.rows_per_small_item, n_q, n_kv, d, bs, splits, scale, ws_small, alibi=alibi,
+                                          window=window)
         if batch.n_items_large:
             n = batch.n_items_large
-            splits = pick_prefill_splits(n, n_q, batch.max_kv_len_large)
+            splits = pick_prefill_splits(n, n_q, seen(batch.max_kv_len_large))
             k.paged_attention_prefill(q, out, kv_layer, batch.block_tables(), batch.items_large(), n, n_q, n_kv, d, bs,
-                                      scale, n_splits=splits, workspace=ws_large if splits > 1 else None, alibi=alibi)
+                                      scale, n_splits=splits, workspace=ws_large if splits > 1 else None, alibi=alibi,
+                                      window=window)
 
     def embed(self, ids, weight, out, pos_weight=None, tok_pos=None, pos_offset=0):
         return self.k.embed(ids, weight, out, pos_weight=pos_weight, tok_pos=tok_pos, pos_offset=pos_offset)

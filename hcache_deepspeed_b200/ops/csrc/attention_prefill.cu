@@ -46,6 +46,7 @@ struct PrefillArgs {
     float* ws_ml;       // [n_items][n_q_heads][n_splits][128][2]
     float* ws_o;        // [n_items][n_q_heads][n_splits][128][D]
     const float* alibi; // [n_q_heads] ALiBi slopes (natural-log units) or nullptr
+    int window;         // sliding-window attention: a query at position p sees keys (p - window, p]; 0 = unlimited
 };
 
 __device__ __forceinline__ float ex2_approx(float x) {
@@ -100,11 +101,14 @@ paged_attn_prefill_kernel(const __grid_constant__ CUtensorMap tmap_q, const __gr
     const int n_live_rows = kPacked ? item.n_q * G : item.n_q;   // rows of the 128-row tile that are ever stored
     const int kv_len = item.pos0 + item.n_q;
     const int tiles_total = (kv_len + kPfTok - 1) / kPfTok;
-    const int tps = (tiles_total + a.n_splits - 1) / a.n_splits;
-    const int eff_splits = (tiles_total + tps - 1) / tps;
+    // sliding window: key tiles wholly before the FIRST query's window are skipped (later rows see even less of them)
+    const int tile_first = a.window > 0 ? max(0, item.pos0 - a.window + 1) / kPfTok : 0;
+    const int tiles_live = tiles_total - tile_first;
+    const int tps = (tiles_live + a.n_splits - 1) / a.n_splits;
+    const int eff_splits = (tiles_live + tps - 1) / tps;
     const int split = blockIdx.z;
     if (split >= eff_splits) return;
-    const int t0 = split * tps;
+    const int t0 = tile_first + split * tps;
     const int n_tiles = min(tiles_total, t0 + tps) - t0;  // tiles of this split: absolute index t0 + ti
     const int bs = a.block_size;
     const int bps = kPfTok / bs;
@@ -241,7 +245,10 @@ paged_attn_prefill_kernel(const __grid_constant__ CUtensorMap tmap_q, const __gr
         auto pair_sync = [&]() { asm volatile("bar.sync %0, 64;" ::"r"(1 + quad) : "memory"); };
         for (int ti = 0; ti < n_tiles; ++ti) {
             const int tok0 = (t0 + ti) * kPfTok + half * HC;
-            const bool need_mask = (t0 + ti) * kPfTok + kPfTok - 1 > item.pos0;  // warp-uniform
+            // warp-uniform: the tile reaches past the first query (causal edge) or starts before the last query's window
+            const bool need_mask = (t0 + ti) * kPfTok + kPfTok - 1 > item.pos0 ||
+                                   (a.window > 0 && (t0 + ti) * kPfTok <= item.pos0 + item.n_q - 1 - a.window);
+            const int win_lo = a.window > 0 ? q_pos - a.window : -(1 << 30);   // keys at or before this position are hidden
             mbar_wait(s_full, ti & 1);
             tc_fence_after();
             if (!quad_live) {
@@ -281,7 +288,7 @@ paged_attn_prefill_kernel(const __grid_constant__ CUtensorMap tmap_q, const __gr
 #pragma unroll
                 for (int j = 0; j < HC; ++j) {
                     const int kv_pos = tok0 + j;
-                    const float sv = (kv_pos <= q_pos && kv_pos < kv_len) ? __uint_as_float(sr[j]) : -INFINITY;
+                    const float sv = (kv_pos <= q_pos && kv_pos < kv_len && kv_pos > win_lo) ? __uint_as_float(sr[j]) : -INFINITY;
                     sr[j] = __float_as_uint(sv);
                     tmax = fmaxf(tmax, sv);
                 }
@@ -514,10 +521,12 @@ static int attention_tc_impl(bool packed, const void* q, void* out, const void* 
     HDS_REQUIRE(n_kv_heads > 0 && n_q_heads % n_kv_heads == 0, "paged_attention_prefill: n_q_heads % n_kv_heads != 0");
     HDS_REQUIRE(dtype == 0 || dtype == 1, "paged_attention_prefill: dtype must be 0 (bf16) or 1 (fp16)");
     const float* alibi = attn_take_alibi();
+    const int window = attn_take_window();
     if (n_items == 0) return HDS_OK;
     PrefillArgs a;
     memset(&a, 0, sizeof(a));
     a.alibi = alibi;
+    a.window = window;
     a.out = out;
     a.block_tables = block_tables;
     a.items = items;
@@ -561,7 +570,7 @@ static int attention_tc_impl(bool packed, const void* q, void* out, const void* 
     if (packed)
         return dtype == 0 ? launch_prefill<128, true, true>(tq, tkv, a, n_items, s)
                           : launch_prefill<128, false, true>(tq, tkv, a, n_items, s);
-    if (head_dim == 128 && block_size <= 64 && alibi == nullptr && prefill64_enabled())   // the 64-key variant has no ALiBi term
+    if (head_dim == 128 && block_size <= 64 && alibi == nullptr && window == 0 && prefill64_enabled())   // no ALiBi / window there
         return dtype == 0 ? launch_prefill64<true>(tq, tkv, a, n_items, s) : launch_prefill64<false>(tq, tkv, a, n_items, s);
     if (head_dim == 128)
         return dtype == 0 ? launch_prefill<128, true>(tq, tkv, a, n_items, s)

@@ -40,6 +40,7 @@ struct AttnArgs {
     float* ws_o;        // [n_items][n_kv_heads][n_splits][R][D]
     int consumer_warps; // 8 (one CTA per SM) or 4 (two CTAs per SM); host-side choice, see attn_pick_warps
     const float* alibi; // [n_q_heads] ALiBi slopes (natural-log units) or nullptr: score += slope * (key pos - query pos)
+    int window;         // sliding-window attention: a query at position p sees keys (p - window, p]; 0 = unlimited
 };
 
 template <int D, int W>
@@ -91,10 +92,13 @@ paged_attn_splitkv_kernel(const __grid_constant__ CUtensorMap tmap_kv, const Att
     const int rows = item.n_q * G;  // <= R (host guarantees)
     const int kv_len = item.pos0 + item.n_q;
     const int tiles_total = (kv_len + kAttnTok - 1) / kAttnTok;
-    const int tps = (tiles_total + a.n_splits - 1) / a.n_splits;
-    const int eff_splits = (tiles_total + tps - 1) / tps;
+    // sliding window: tiles that lie wholly before the first query's window are never loaded
+    const int tile_first = a.window > 0 ? max(0, item.pos0 - a.window + 1) / kAttnTok : 0;
+    const int tiles_live = tiles_total - tile_first;
+    const int tps = (tiles_live + a.n_splits - 1) / a.n_splits;
+    const int eff_splits = (tiles_live + tps - 1) / tps;
     if (split >= eff_splits) return;
-    const int t0 = split * tps;
+    const int t0 = tile_first + split * tps;
     const int t1 = min(tiles_total, t0 + tps);
     const int bs = a.block_size;
 
@@ -216,7 +220,8 @@ paged_attn_splitkv_kernel(const __grid_constant__ CUtensorMap tmap_kv, const Att
                 for (int r = 0; r < R; ++r) {
                     float sc = part[r] + __shfl_xor_sync(0xffffffffu, part[r], 16);
                     const int q_pos = item.pos0 + r / G;
-                    const bool ok = (j < n_mine) && (tok0 + rt <= q_pos) && (r < rows);
+                    const bool ok = (j < n_mine) && (tok0 + rt <= q_pos) && (r < rows) &&
+                                    (a.window <= 0 || tok0 + rt > q_pos - a.window);
                     sc = ok ? fmaf(slope[r], static_cast<float>(tok0 + rt - q_pos), sc) : -INFINITY;
                     float mx = sc;
 #pragma unroll
@@ -388,16 +393,28 @@ static inline int attn_pick_warps(int64_t ctas) {
 
 // ALiBi slopes for the NEXT paged-attention launch of this thread (either kernel family); consumed by that launch.
 static thread_local const float* g_next_alibi = nullptr;
+static thread_local int g_next_window = 0;
 const float* hds::attn_take_alibi() {
     const float* p = g_next_alibi;
     g_next_alibi = nullptr;
     return p;
+}
+int hds::attn_take_window() {
+    const int w = g_next_window;
+    g_next_window = 0;
+    return w;
 }
 
 using namespace hds;
 
 extern "C" int hds_attention_next_alibi(const float* slopes) {
     g_next_alibi = slopes;
+    return HDS_OK;
+}
+
+extern "C" int hds_attention_next_window(int window) {
+    HDS_REQUIRE(window >= 0, "hds_attention_next_window: window >= 0 (0 = unlimited)");
+    g_next_window = window;
     return HDS_OK;
 }
 
@@ -416,6 +433,7 @@ extern "C" int hds_paged_attention_splitkv(const void* q, void* out, const void*
                                                 int block_size, int n_splits, float scale, void* workspace,
                                                 int64_t workspace_bytes, int dtype, void* stream) {
     const float* alibi = attn_take_alibi();
+    const int window = attn_take_window();
     HDS_REQUIRE(head_dim == 64 || head_dim == 128, "paged_attention_splitkv: head_dim must be 64 or 128");
     HDS_REQUIRE(block_size == 16 || block_size == 32 || block_size == 64 || block_size == 128,
                 "paged_attention_splitkv: block_size must be 16/32/64/128");
@@ -443,6 +461,7 @@ extern "C" int hds_paged_attention_splitkv(const void* q, void* out, const void*
     a.n_splits = n_splits;
     a.scale_log2 = scale * 1.4426950408889634f;
     a.alibi = alibi;
+    a.window = window;
     const int64_t units = static_cast<int64_t>(n_items) * n_kv_heads;
     char* ws = reinterpret_cast<char*>(workspace);
     a.counters = reinterpret_cast<int32_t*>(ws);

@@ -216,5 +216,6 @@ inline int make_tmap_3d_16b(CUtensorMap* map, const void* base, uint64_t d0, uin
 // ALiBi slopes armed by hds_attention_next_alibi for the next paged-attention launch of this thread (defined in
 // attention_splitkv.cu); returns them once, then nullptr.
 const float* attn_take_alibi();
+int attn_take_window();   // same for hds_attention_next_window (0 = no sliding window)
 
 }  // namespace hds

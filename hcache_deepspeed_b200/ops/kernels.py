@@ -374,8 +374,11 @@ def splitkv_workspace_bytes(n_items: int, n_q_heads: int, n_kv_heads: int, head_
                                                                              max_splits, rows_per_item))
 
 
-def _arm_alibi(lib, alibi: Optional[torch.Tensor], n_q_heads: int) -> None:
-    """ALiBi slopes for the next attention launch of this thread (``hds_attention_next_alibi``; consumed by that launch)."""
+def _arm_alibi(lib, alibi: Optional[torch.Tensor], n_q_heads: int, window: int = 0) -> None:
+    """ALiBi slopes / sliding window for the next attention launch of this thread (``hds_attention_next_alibi``,
+    ``hds_attention_next_window``; both are consumed by that launch)."""
+    if window:
+        native.check(lib.hds_attention_next_window(int(window)), "hds_attention_next_window")
     if alibi is None:
         return
     assert alibi.dtype == torch.float32 and alibi.is_cuda and alibi.is_contiguous() and alibi.numel() == n_q_heads
@@ -385,11 +388,12 @@ def _arm_alibi(lib, alibi: Optional[torch.Tensor], n_q_heads: int) -> None:
 def paged_attention_splitkv(q: torch.Tensor, out: torch.Tensor, kv_cache_layer: torch.Tensor,
                             block_tables: torch.Tensor, items: torch.Tensor, n_items: int, rows_per_item: int,
                             n_q_heads: int, n_kv_heads: int, head_dim: int, block_size: int, n_splits: int,
-                            scale: float, workspace: Optional[torch.Tensor], alibi: Optional[torch.Tensor] = None) -> None:
+                            scale: float, workspace: Optional[torch.Tensor], alibi: Optional[torch.Tensor] = None,
+                            window: int = 0) -> None:
     """kv_cache_layer: [blocks, 2, kvh, bs, d]; items: int32 [n, 4] = (seq, q_row0, n_q, pos0). ``alibi``: fp32 [n_q_heads]
-    slopes; score += slope * (key position - query position)."""
+    slopes; score += slope * (key position - query position). ``window``: sliding-window attention, keys (p - window, p]."""
     lib = native.cuda_lib()
-    _arm_alibi(lib, alibi, n_q_heads)
+    _arm_alibi(lib, alibi, n_q_heads, window)
     rc = lib.hds_paged_attention_splitkv(_p(q), _p(out), _p(kv_cache_layer), kv_cache_layer.shape[0], _p(block_tables),
                                          block_tables.stride(0), _p(items), n_items, rows_per_item, n_q_heads,
                                          n_kv_heads, head_dim, block_size, n_splits, scale, _p(workspace),
@@ -407,11 +411,12 @@ def paged_attention_prefill(q: torch.Tensor, out: torch.Tensor, kv_cache_layer: 
                             block_tables: torch.Tensor, items: torch.Tensor, n_items: int, n_q_heads: int,
                             n_kv_heads: int, head_dim: int, block_size: int, scale: float, n_splits: int = 1,
                             workspace: Optional[torch.Tensor] = None, packed: bool = False,
-                            alibi: Optional[torch.Tensor] = None) -> None:
+                            alibi: Optional[torch.Tensor] = None, window: int = 0) -> None:
     """tcgen05 paged attention. ``packed``: grouped-query decode form — one CTA per (item, KV head) whose MMA rows are
-    the group's (token, query head) pairs (``hds_paged_attention_packed``). ``alibi``: fp32 [n_q_heads] slopes."""
+    the group's (token, query head) pairs (``hds_paged_attention_packed``). ``alibi``: fp32 [n_q_heads] slopes;
+    ``window``: sliding-window attention."""
     lib = native.cuda_lib()
-    _arm_alibi(lib, alibi, n_q_heads)
+    _arm_alibi(lib, alibi, n_q_heads, window)
     fn = lib.hds_paged_attention_packed if packed else lib.hds_paged_attention_prefill
     rc = fn(_p(q), _p(out), _p(kv_cache_layer), kv_cache_layer.shape[0], _p(block_tables),
                                          block_tables.stride(0), _p(items), n_items, q.shape[0], n_q_heads, n_kv_heads,

@@ -44,6 +44,7 @@ def _declare_cuda(lib: ctypes.CDLL) -> None:
         "hds_norm_tp": [I, I, I, P, L, P, P, I, P, P, P, L, P, P, I, I, I, P, P, I, F, I, I, P],
         "hds_fp8_next_weight_format": [I],
         "hds_attention_next_alibi": [P],
+        "hds_attention_next_window": [I],
         "hds_host_buffer_alloc": [L, I, I, P],
         "hds_host_buffer_device_ptr": [P, P],
         "hds_host_buffer_free": [P],

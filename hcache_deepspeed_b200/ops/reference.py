@@ -90,9 +90,10 @@ def gather_kv(kv_cache_layer: torch.Tensor, block_table_row: torch.Tensor, kv_le
 
 def paged_attention(q: torch.Tensor, kv_cache_layer: torch.Tensor, block_tables: torch.Tensor, items: torch.Tensor,
                     n_q_heads: int, n_kv_heads: int, scale: float, out: Optional[torch.Tensor] = None,
-                    alibi: Optional[torch.Tensor] = None) -> torch.Tensor:
+                    alibi: Optional[torch.Tensor] = None, window: int = 0) -> torch.Tensor:
     """q: [T, n_q_heads, d]; items: int32 [n, 4] rows (seq, q_row0, n_q, pos0). Causal over absolute positions.
-    ``alibi``: [n_q_heads] slopes, score += slope * (key position - query position)."""
+    ``alibi``: [n_q_heads] slopes, score += slope * (key position - query position). ``window`` > 0: a query at position p
+    sees the keys (p - window, p] only."""
     T, _, d = q.shape
     if out is None:
         out = torch.zeros_like(q)
@@ -109,6 +110,8 @@ def paged_attention(q: torch.Tensor, kv_cache_layer: torch.Tensor, block_tables:
         if alibi is not None:
             s = s + alibi.float().to(s.device)[:, None, None] * (kv_pos - q_pos).float()
         s = s.masked_fill(kv_pos > q_pos, float("-inf"))
+        if window:
+            s = s.masked_fill(kv_pos <= q_pos - window, float("-inf"))
         p = torch.softmax(s, dim=-1)
         out[q_row0:q_row0 + n_q] = torch.einsum("hqk,khd->qhd", p, v).to(out.dtype)
     return out

@@ -234,6 +234,11 @@ int hds_host_buffer_free(void* host_ptr);
  * before the softmax, then the setting is cleared. (hds_paged_attention_splitkv_static ignores it.) */
 int hds_attention_next_alibi(const float* slopes);
 
+/* Sliding-window attention (Mistral, Phi-3, GPT-Neo's local layers): the NEXT paged-attention launch of the calling
+ * thread lets a query at position p see the keys (p - window, p] only; key tiles wholly outside the window are not
+ * loaded. 0 = unlimited. Cleared by that launch. */
+int hds_attention_next_window(int window);
+
 /* tcgen05 paged attention for items with up to 128 query tokens (prefill / chunked continuation): QK^T and
  * PV on the tensor cores with TMEM accumulators, TMA page gathers, online softmax in registers.
  * n_q_rows = total rows of q (bounds the Q tensor map). n_splits > 1 splits each item's KV range over several

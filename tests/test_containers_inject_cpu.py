@@ -81,7 +81,7 @@ def test_init_inference_kernel_inject_uses_containers():
     torch.manual_seed(0)
     ids = torch.randint(1, 50, (1, 6))
     # families / variants outside the ragged executor: block-by-block injection through the container policies
-    for name in ("gptneo", "gpt2_scaled"):
+    for name in ("gpt2_scaled", ):
         model = AutoModelForCausalLM.from_config(CAUSAL[name]()).eval().float()
         with torch.no_grad():
             want = model(ids).logits
@@ -90,7 +90,7 @@ def test_init_inference_kernel_inject_uses_containers():
         with torch.no_grad():
             torch.testing.assert_close(engine(ids).logits, want, rtol=1e-4, atol=1e-5)
     # GPT-2 / GPT-J / GPT-NeoX / Bloom are lifted whole onto the ragged executor (paged KV, the sm_100a kernels on a GPU)
-    for name in ("gpt2", "gptj", "gptneox", "gptneox_sequential", "bloom"):
+    for name in ("gpt2", "gptj", "gptneox", "gptneox_sequential", "bloom", "gptneo"):
         model = AutoModelForCausalLM.from_config(CAUSAL[name]()).eval().float()
         with torch.no_grad():
             want = model(ids).logits

@@ -300,6 +300,16 @@ def _hf_model(kind):
         return GPTNeoXForCausalLM(GPTNeoXConfig(vocab_size=2048, hidden_size=512, num_hidden_layers=3, num_attention_heads=4,
                                                 intermediate_size=2048, rotary_pct=0.25, max_position_embeddings=1024,
                                                 hidden_dropout=0.0, attention_dropout=0.0)).eval()
+    if kind == "gpt_neo":       # local layers: window 64 < the 200-token prompt
+        from transformers import GPTNeoConfig, GPTNeoForCausalLM
+        return GPTNeoForCausalLM(GPTNeoConfig(vocab_size=2048, hidden_size=512, num_layers=4, num_heads=8, window_size=64,
+                                              attention_types=[[["global", "local"], 2]], max_position_embeddings=1024,
+                                              resid_dropout=0.0, embed_dropout=0.0, attention_dropout=0.0)).eval()
+    if kind == "mistral_window":
+        from transformers import MistralConfig, MistralForCausalLM
+        return MistralForCausalLM(MistralConfig(vocab_size=2048, hidden_size=512, intermediate_size=1408, num_hidden_layers=3,
+                                                num_attention_heads=4, num_key_value_heads=2, sliding_window=96,
+                                                max_position_embeddings=1024)).eval()
     if kind == "bloom":
         from transformers import BloomConfig, BloomForCausalLM
         return BloomForCausalLM(BloomConfig(vocab_size=2048, hidden_size=768, n_layer=3, n_head=6, hidden_dropout=0.0,
@@ -316,7 +326,8 @@ def _hf_model(kind):
 
 
 # gpt2 / gptj / gpt_neox: the families the reference serves through its v1 transformer_inference op only
-@pytest.mark.parametrize("kind", ["opt", "llama", "gpt2", "gptj", "gpt_neox", "bloom", "falcon_alibi"])
+@pytest.mark.parametrize("kind", ["opt", "llama", "gpt2", "gptj", "gpt_neox", "bloom", "falcon_alibi", "gpt_neo",
+                                  "mistral_window"])
 def test_v1_init_inference_kernel_inject_gpu(kind):
     """``init_inference(replace_with_kernel_inject=True)`` on the GPU (v1 API): the injected engine runs the sm_100a
     kernels, its logits track the HuggingFace model's fp32 logits for a prompt and for a continuation over the live KV

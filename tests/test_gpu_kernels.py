@@ -474,6 +474,67 @@ def test_attention_alibi_all_kernels(dtype):
     torch.testing.assert_close(out.float(), want.float(), **tol(dtype))
 
 
+@pytest.mark.parametrize("dtype", DTYPES)
+@pytest.mark.parametrize("window", [1, 100, 128, 1000])
+def test_attention_sliding_window_all_kernels(dtype, window):
+    """Sliding-window attention (``hds_attention_next_window``): keys (p - window, p] only, key tiles before the window
+    skipped, in the split-KV decode kernel (split and unsplit, one and several rows), the tensor-core prefill kernel and the
+    head-packed GQA kernel; combined with ALiBi once; consumed by ONE launch."""
+    sc = lambda d: 1.0 / math.sqrt(d)
+    for n_q_heads, n_kv, d, bs, rows in ((8, 8, 128, 64, 1), (12, 12, 64, 128, 1), (16, 4, 128, 64, 1), (4, 4, 128, 64, 8)):
+        specs = [(0, rows), (5, rows), (127, 1), (1000, rows), (4095, 1), (333, 1)]
+        q, cache, tables, items = build_paged_problem(specs, n_q_heads, n_kv, d, bs, dtype, seed=21)
+        items_t = torch.tensor(items, dtype=torch.int32, device="cuda")
+        R = rows * (n_q_heads // n_kv)
+        want = ref.paged_attention(q, cache, tables, items_t.cpu(), n_q_heads, n_kv, sc(d), window=window)
+        plain = ref.paged_attention(q, cache, tables, items_t.cpu(), n_q_heads, n_kv, sc(d))
+        for n_splits in (1, 3):
+            ws = torch.zeros(max(K().splitkv_workspace_bytes(len(items), n_q_heads, n_kv, d, n_splits, R), 16), dtype=torch.uint8,
+                             device="cuda")
+            out = torch.zeros_like(q)
+            for _ in range(2):
+                out.zero_()
+                K().paged_attention_splitkv(q, out, cache, tables, items_t, len(items), R, n_q_heads, n_kv, d, bs, n_splits, sc(d),
+                                            ws, window=window)
+                torch.testing.assert_close(out.float(), want.float(), **tol(dtype))
+            out.zero_()
+            K().paged_attention_splitkv(q, out, cache, tables, items_t, len(items), R, n_q_heads, n_kv, d, bs, n_splits, sc(d), ws)
+            torch.testing.assert_close(out.float(), plain.float(), **tol(dtype))
+    for n_q_heads, n_kv, d, bs in ((4, 4, 128, 64), (6, 6, 64, 128), (8, 2, 128, 16)):
+        specs = [(0, 128), (0, 17), (100, 64), (1000, 128), (4000, 96), (63, 1), (300, 128)]
+        q, cache, tables, items = build_paged_problem(specs, n_q_heads, n_kv, d, bs, dtype, seed=22)
+        items_t = torch.tensor(items, dtype=torch.int32, device="cuda")
+        want = ref.paged_attention(q, cache, tables, items_t.cpu(), n_q_heads, n_kv, sc(d), window=window)
+        out = torch.zeros_like(q)
+        K().paged_attention_prefill(q, out, cache, tables, items_t, len(items), n_q_heads, n_kv, d, bs, sc(d), window=window)
+        torch.testing.assert_close(out.float(), want.float(), **tol(dtype))
+        ws = torch.zeros(K().prefill_workspace_bytes(len(items), n_q_heads, d, 3), dtype=torch.uint8, device="cuda")
+        for _ in range(2):
+            out.zero_()
+            K().paged_attention_prefill(q, out, cache, tables, items_t, len(items), n_q_heads, n_kv, d, bs, sc(d), n_splits=3,
+                                        workspace=ws, window=window)
+            torch.testing.assert_close(out.float(), want.float(), **tol(dtype))
+        slopes = ref.alibi_slopes(n_q_heads).cuda()
+        want_a = ref.paged_attention(q, cache, tables, items_t.cpu(), n_q_heads, n_kv, sc(d), window=window, alibi=slopes)
+        out.zero_()
+        K().paged_attention_prefill(q, out, cache, tables, items_t, len(items), n_q_heads, n_kv, d, bs, sc(d), window=window,
+                                    alibi=slopes)
+        torch.testing.assert_close(out.float(), want_a.float(), **tol(dtype))
+    n_q_heads, n_kv, d, bs = 32, 4, 128, 64
+    specs = [(0, 1), (100, 1), (1000, 1), (4000, 1), (5, 3), (700, 6)]
+    q, cache, tables, items = build_paged_problem(specs, n_q_heads, n_kv, d, bs, dtype, seed=23)
+    items_t = torch.tensor(items, dtype=torch.int32, device="cuda")
+    want = ref.paged_attention(q, cache, tables, items_t.cpu(), n_q_heads, n_kv, sc(d), window=window)
+    out = torch.zeros_like(q)
+    K().paged_attention_prefill(q, out, cache, tables, items_t, len(items), n_q_heads, n_kv, d, bs, sc(d), packed=True, window=window)
+    torch.testing.assert_close(out.float(), want.float(), **tol(dtype))
+    ws = torch.zeros(K().prefill_workspace_bytes(len(items), n_kv, d, 4), dtype=torch.uint8, device="cuda")
+    out.zero_()
+    K().paged_attention_prefill(q, out, cache, tables, items_t, len(items), n_q_heads, n_kv, d, bs, sc(d), packed=True, n_splits=4,
+                                workspace=ws, window=window)
+    torch.testing.assert_close(out.float(), want.float(), **tol(dtype))
+
+
 def test_attention_prefill_64_key_tiles_subprocess():
     """The opt-in 64-key-tile / two-CTAs-per-SM shape of the tensor-core attention kernel (HDS_PREFILL_TILE=64, read once per
     process): the prefill attention tests of this file are re-run in a child process with the variable set."""

@@ -62,12 +62,20 @@ def _tiny(family):
         return T.FalconForCausalLM(T.FalconConfig(hidden_size=128, num_hidden_layers=2, num_attention_heads=4, vocab_size=300,
                                                   multi_query=False, parallel_attn=False, new_decoder_architecture=False,
                                                   alibi=True, bias=True))
+    if family == "gpt_neo":       # local layers with a window shorter than the test prompts
+        return T.GPTNeoForCausalLM(T.GPTNeoConfig(hidden_size=128, num_layers=2, num_heads=4, vocab_size=300, window_size=8,
+                                                  attention_types=[[["global", "local"], 1]], max_position_embeddings=512))
+    if family == "mistral_window":
+        return T.MistralForCausalLM(T.MistralConfig(intermediate_size=256, num_key_value_heads=2, sliding_window=10, **common))
+    if family == "phi3_window":
+        return T.Phi3ForCausalLM(T.Phi3Config(intermediate_size=256, num_key_value_heads=2, pad_token_id=0, sliding_window=12,
+                                              **common))
     raise KeyError(family)
 
 
 FAMILIES = ["llama", "llama_mha_bias", "mistral", "qwen2", "opt", "falcon_mqa", "falcon_new", "phi", "phi3", "mixtral", "qwen2_moe",
             "gpt2", "gptj", "gpt_neox", "gpt_neox_sequential",
-            "bloom", "bloom_6heads", "falcon_alibi"]
+            "bloom", "bloom_6heads", "falcon_alibi", "gpt_neo", "mistral_window", "phi3_window"]
 
 
 @pytest.mark.parametrize("family", FAMILIES)
