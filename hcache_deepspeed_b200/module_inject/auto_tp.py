@@ -18,15 +18,29 @@ from torch import nn
 
 from .. import comm as dist
 from ..utils.logging import logger
-from .fusedqkv_utils import prepare_tp_fused_qkvw, require_tp_fused_qkvw, shard_chunk_mlp
+from .fusedqkv_utils import fused_qkv_layout, prepare_tp_fused_qkvw, require_tp_fused_qkvw, shard_chunk_mlp
 from .layers import LinearAllreduce, LinearLayer, LmHeadLinearAllreduce
 from .tp_shard import get_shard_size, get_shard_size_list, set_n_embd, set_num_kv_heads
 
-ALL_REDUCE_NAMES = ("o_proj", "out_proj", "dense_4h_to_h", "down_proj", "fc2", "c_proj", "attention.dense", "self_attention.dense",
-                    "wo", "w2", "dense_out", "attn.proj", "mlp.dense_4h_to_h", "attention.output.dense", "output.dense")
+ALL_REDUCE_NAMES = ("o_proj", "out_proj", "dense_4h_to_h", "down_proj", "fc2", "fc_out", "c_proj", "attention.dense",
+                    "self_attention.dense", "self_attn.dense", "wo", "w2", "dense_out", "attn.proj", "mlp.dense_4h_to_h",
+                    "attention.output.dense", "output.dense")
 UNSUPPORTED = ("deberta", "flaubert", "fsmt", "gpt2-as-conv1d", "led", "longformer", "xlm", "xlnet")
 HEAD_ATTRS = ("num_heads", "num_attention_heads", "num_attn_heads", "n_heads", "n_head", "num_kv_heads", "num_key_value_heads",
-              "num_kv", "all_head_size", "embed_dim", "hidden_size", "n_embd", "num_key_value_groups")
+              "num_kv", "all_head_size", "embed_dim", "hidden_size", "n_embd", "split_size", "num_key_value_groups")
+
+
+def is_linear(m: nn.Module) -> bool:
+    """nn.Linear, or HuggingFace's ``Conv1D`` (GPT-2: the same affine map with the weight stored [in, out])."""
+    return isinstance(m, nn.Linear) or (type(m).__name__ == "Conv1D" and hasattr(m, "nf") and hasattr(m, "weight"))
+
+
+def linear_weight_bias(m: nn.Module):
+    """(weight [out, in], bias) of a linear-like module."""
+    w = m.weight.data
+    if not isinstance(m, nn.Linear):
+        w = w.t()
+    return w, (m.bias.data if getattr(m, "bias", None) is not None else None)
 
 
 class ReplaceWithTensorSlicing:
@@ -108,6 +122,8 @@ class AutoTP:
         self.mp_size, self.mp_group, self.globals_rank = None, None, 0
         self.keep_module_on_host = keep_module_on_host
         self.conv_linear_layer = False
+        self.default_heads = (None, None)       # (query heads, KV heads) of the model config: for attention modules that
+                                                # keep no head-count attribute of their own (GPT-NeoX)
 
     # ---- discovery -------------------------------------------------------------------------------------
     @staticmethod
@@ -147,22 +163,18 @@ class AutoTP:
 
     @staticmethod
     def tp_parser(model) -> List[Tuple[nn.Module, List[str]]]:
-        """[(block, [names of its linears that need an all-reduce])]."""
+        """[(block, [names of its linears that need an all-reduce])]. A linear is row-parallel when its name says so
+        (``o_proj``, ``fc2``, ``c_proj``, ...); in a sub-module with several linears and no such name the LAST one is taken
+        (the projection back to the residual stream: Phi's ``self_attn.dense``, GPT-J's ``mlp.fc_out`` style layouts)."""
         assert AutoTP.supported(model), "AutoTP not supported for model. Please use kernel injection since container policy for model exists."
         policy_list = []
         for block in AutoTP.get_module_list(model):
-            linears = [n for n, m in block.named_modules() if isinstance(m, nn.Linear)]
-            gems = []
-            for n in linears:
-                leaf = n.split(".")[-1]
-                if any(n.endswith(k) or leaf == k for k in ALL_REDUCE_NAMES):
-                    gems.append(n)
-            if not gems and linears:
-                # fall back on structure: the last Linear of each direct sub-module that holds several linears
-                for cname, child in block.named_children():
-                    cl = [n for n, m in child.named_modules() if isinstance(m, nn.Linear)]
-                    if len(cl) >= 2:
-                        gems.append(cname + "." + cl[-1])
+            linears = [n for n, m in block.named_modules() if is_linear(m) and n]
+            gems = [n for n in linears if any(n.endswith(k) or n.split(".")[-1] == k for k in ALL_REDUCE_NAMES)]
+            for cname, child in block.named_children():
+                cl = [n for n, m in child.named_modules() if is_linear(m) and n]
+                if len(cl) >= 2 and not any(g.startswith(cname + ".") for g in gems):
+                    gems.append(cname + "." + cl[-1])
             if gems:
                 AutoTP.update_policy_list(policy_list, block, gems)
         assert policy_list, "AutoTP not supported for model: no row-parallel linears found. Please use kernel injection."
@@ -180,16 +192,17 @@ class AutoTP:
         start = sum(sizes[:self.rank])
         return t.narrow(dim, start, sizes[self.rank]).clone().contiguous()
 
-    def _replace(self, child: nn.Linear, name: str, full_name: str, block) -> nn.Module:
+    def _replace(self, child: nn.Module, name: str, full_name: str, block) -> nn.Module:
         if getattr(child, "replaced", False):
             return child
-        w, b = child.weight.data, (child.bias.data if child.bias is not None else None)
+        w, b = linear_weight_bias(child)
         if any(full_name.endswith(g) or name == g for g in self.all_reduce_linears):
             new = LinearAllreduce(self._slice(w, 1, full_name), b.clone() if b is not None else None, self.mp_group)
         elif require_tp_fused_qkvw(full_name, self.mp_size):
             heads = self._heads_of(block)
-            nw = prepare_tp_fused_qkvw(type(block).__name__, w, self.mp_size, self.rank, heads[0], heads[1]).clone()
-            nb = prepare_tp_fused_qkvw(type(block).__name__, b, self.mp_size, self.rank, heads[0], heads[1]).clone() if b is not None else None
+            kind = fused_qkv_layout(block)
+            nw = prepare_tp_fused_qkvw(kind, w, self.mp_size, self.rank, heads[0], heads[1]).clone()
+            nb = prepare_tp_fused_qkvw(kind, b, self.mp_size, self.rank, heads[0], heads[1]).clone() if b is not None else None
             new = LinearLayer(weight=nw, bias=nb, mp_group=self.mp_group)
         elif any(k in full_name for k in ("gate_up_proj", "dense_h_to_4h_fused")):
             nw, nb = shard_chunk_mlp(w, b, self.rank, self.mp_size)
@@ -200,7 +213,19 @@ class AutoTP:
         return new
 
     def _heads_of(self, block):
+        """(query heads, KV heads) of the block BEFORE sharding (``update_mp_params`` keeps the originals)."""
         cfg_heads, cfg_kv = None, None
+        for m in block.modules():
+            orig = getattr(m, "_autotp_orig", None)
+            if orig:
+                for a in ("num_heads", "num_attention_heads", "n_head", "n_heads"):
+                    if a in orig and cfg_heads is None:
+                        cfg_heads = orig[a]
+                for a in ("num_key_value_heads", "num_kv_heads", "num_kv"):
+                    if a in orig and cfg_kv is None:
+                        cfg_kv = orig[a]
+        if cfg_heads is not None:
+            return cfg_heads, cfg_kv
         for m in block.modules():
             for a in ("num_heads", "num_attention_heads", "n_head", "n_heads"):
                 if isinstance(getattr(m, a, None), int) and cfg_heads is None:
@@ -208,31 +233,59 @@ class AutoTP:
             for a in ("num_key_value_heads", "num_kv_heads", "num_kv"):
                 if isinstance(getattr(m, a, None), int) and cfg_kv is None:
                     cfg_kv = getattr(m, a)
+        if cfg_heads is None:
+            cfg_heads = self.default_heads[0]
+        if cfg_kv is None:
+            cfg_kv = self.default_heads[1]
         return cfg_heads, cfg_kv
 
     def update_mp_params(self, child):
         """Divide head-count / width attributes of attention modules by the TP degree."""
         if getattr(child, "_autotp_updated", False):
             return
+        child._autotp_orig = {a: getattr(child, a) for a in HEAD_ATTRS if isinstance(getattr(child, a, None), int)}
         for a in HEAD_ATTRS:
             v = getattr(child, a, None)
             if isinstance(v, int) and a != "num_key_value_groups":
+                if a in ("num_kv_heads", "num_key_value_heads", "num_kv") and v < self.mp_size:
+                    continue        # fewer KV heads than ranks (multi-query): K / V stay replicated
                 try:
                     setattr(child, a, get_shard_size(v, self.mp_size, rank=self.rank))
                 except AttributeError:
                     pass
+        # modules that read head counts from their (shared) config at run time (Phi-3: ``config.num_attention_heads`` in
+        # forward) get a private shallow copy of it with this rank's counts
+        cfg = getattr(child, "config", None)
+        if cfg is not None and any(isinstance(getattr(cfg, a, None), int) for a in ("num_attention_heads", "n_head")):
+            import copy
+            local = copy.copy(cfg)
+            for a in ("num_attention_heads", "n_head", "num_key_value_heads", "num_kv_heads"):
+                v = getattr(cfg, a, None)
+                if isinstance(v, int) and not (a in ("num_key_value_heads", "num_kv_heads") and v < self.mp_size):
+                    try:
+                        setattr(local, a, get_shard_size(v, self.mp_size, rank=self.rank))
+                    except AttributeError:
+                        pass
+            try:
+                child.config = local
+            except AttributeError:
+                pass
         child._autotp_updated = True
 
     def _replace_module(self, r_module, block=None, prev_name: str = "", prev_class_name: str = ""):
         for name, child in list(r_module.named_children()):
             full = f"{prev_name}.{name}" if prev_name else name
-            if isinstance(child, nn.Linear):
+            if is_linear(child):
                 setattr(r_module, name, self._replace(child, name, full, block if block is not None else r_module))
             elif isinstance(child, nn.Embedding) and False:
                 pass
             else:
-                if any(hasattr(child, a) for a in ("num_heads", "num_attention_heads", "n_head", "n_heads")) and \
-                        any(isinstance(m, nn.Linear) for m in child.children()):
+                has_counts = any(hasattr(child, a) for a in ("num_heads", "num_attention_heads", "n_head", "n_heads"))
+                if not has_counts and "attention" in type(child).__name__.lower().replace("attn", "attention"):
+                    # attention modules that keep only KV-head counts / read the rest from their config (Phi-3)
+                    has_counts = any(hasattr(child, a) for a in ("num_key_value_heads", "num_kv_heads")) or \
+                        isinstance(getattr(getattr(child, "config", None), "num_attention_heads", None), int)
+                if has_counts and any(is_linear(m) for m in child.children()):
                     self.update_mp_params(child)
                 self._replace_module(child, block if block is not None else r_module, full, type(child).__name__)
         return r_module
@@ -262,9 +315,16 @@ class AutoTP:
             if cfg is not None and isinstance(getattr(cfg, a, None), int):
                 kv = getattr(cfg, a)
                 break
+        if kv is not None and 1 < kv < mp_size:
+            # every rank raises the same error before any collective: a grouped-query model cannot give each rank a whole KV
+            # head here (multi-query models, kv = 1, keep K / V replicated instead)
+            raise ValueError(f"AutoTP: {kv} key/value heads cannot be split over {mp_size} ranks; use tp_size <= {kv}, or kernel "
+                             f"injection (the ragged executor replicates KV heads across ranks)")
         set_num_kv_heads(kv)
         if cfg is not None and isinstance(getattr(cfg, "hidden_size", None), int):
             set_n_embd(cfg.hidden_size)
+        n_q = next((getattr(cfg, a) for a in ("num_attention_heads", "n_head", "num_heads", "n_heads")
+                    if cfg is not None and isinstance(getattr(cfg, a, None), int)), None)
         policies = AutoTP.tp_parser(model)
         by_type: Dict[str, List[str]] = {type(m).__name__: gems for m, gems in policies}
         for module in model.modules():
@@ -273,8 +333,10 @@ class AutoTP:
                 at = AutoTP(model, by_type[tname], "", None, None, type(module))
                 at.set_tensor_parallel_config(mp_size, mp_group)
                 at.rank = rank
+                at.default_heads = (n_q, kv)
                 at._replace_module(module)
                 module._autotp_done = True
+        _patch_alibi_builders(model, mp_size, rank)
         if replace_lm_head:
             at = AutoTP(model, [], "", None, None, None)
             at.set_tensor_parallel_config(mp_size, mp_group)
@@ -282,3 +344,14 @@ class AutoTP:
             at._replace_last_linear_module(model)
         logger.info(f"AutoTP: sharded {sum(len(g) for g in by_type.values())} row-parallel linear kinds over {mp_size} ranks")
         return model
+
+
+def _patch_alibi_builders(model: nn.Module, mp_size: int, rank: int) -> None:
+    """BLOOM-style models build an ALiBi tensor for ALL heads in the model's forward; after sharding every rank needs the
+    rows of its own heads (ref: auto_tp_model_utils.py build_bloom_alibi_tensor, replace_module.py:309-313)."""
+    from .auto_tp_model_utils import build_bloom_alibi_tensor
+    for m in model.modules():
+        if hasattr(m, "build_alibi_tensor") and type(m).__name__ in ("BloomModel", ):
+            def build(attention_mask, num_heads, dtype, _m=m):
+                return build_bloom_alibi_tensor(attention_mask, num_heads, dtype, mp_size=mp_size, mp_rank=rank)
+            m.build_alibi_tensor = build

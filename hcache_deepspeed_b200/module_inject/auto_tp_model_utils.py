@@ -20,17 +20,22 @@ def _slopes(n_heads: int) -> torch.Tensor:
     return s
 
 
-def build_bloom_alibi_tensor(attention_mask: torch.Tensor, num_heads: int, dtype: torch.dtype) -> torch.Tensor:
-    """``[batch * local_heads, 1, seq]`` ALiBi bias; under tensor parallelism only this rank's head slice."""
+def build_bloom_alibi_tensor(attention_mask: torch.Tensor, num_heads: int, dtype: torch.dtype, mp_size=None,
+                             mp_rank=None) -> torch.Tensor:
+    """``[batch * local_heads, 1, seq]`` ALiBi bias; under tensor parallelism only this rank's head slice (the same
+    head split as the fused-QKV slicing: ``tp_shard.get_shard_size_list``)."""
+    from .tp_shard import get_shard_size_list
     batch, seq = attention_mask.shape
     slopes = _slopes(num_heads).to(attention_mask.device)
     pos = ((attention_mask.cumsum(dim=-1) - 1) * attention_mask)[:, None, :]
     alibi = slopes[None, :, None] * pos                       # [batch, heads, seq]
-    if dist.is_initialized() and dist.get_world_size() > 1:
-        per = num_heads // dist.get_world_size()
-        r = dist.get_rank()
-        alibi = alibi[:, r * per:(r + 1) * per]
-        num_heads = per
+    if mp_size is None and dist.is_initialized():
+        mp_size, mp_rank = dist.get_world_size(), dist.get_rank()
+    if mp_size and mp_size > 1:
+        sizes = get_shard_size_list(num_heads, mp_size)
+        start = sum(sizes[:mp_rank])
+        alibi = alibi[:, start:start + sizes[mp_rank]]
+        num_heads = sizes[mp_rank]
     return alibi.reshape(batch * num_heads, 1, seq).to(dtype)
 
 

@@ -9,8 +9,36 @@ from .tp_shard import get_shard_size, get_shard_size_list
 FUSED_QKV_TYPES = {
     "CodeGenBlock": "codegentype", "BloomBlock": "bloomtype", "GLMBlock": "glmtype", "MPTBlock": "glmtype",
     "MptBlock": "glmtype", "BaichuanLayer": "glmtype", "QWenBlock": "qwentype", "FalconDecoderLayer": "bloomtype",
-    "GPTBigCodeBlock": "bigcodetype", "DecoderLayer": "glmtype", "Phi3DecoderLayer": "phi3type",
+    "GPTBigCodeBlock": "bigcodetype", "DecoderLayer": "glmtype", "Phi3DecoderLayer": "phi3type", "GPTNeoXLayer": "bloomtype",
+    "GPT2Block": "glmtype",
 }
+
+
+def fused_qkv_layout(block) -> str:
+    """Layout name of ``block``'s fused QKV weight. Falcon has three, chosen by its attention module's flags: grouped
+    [kv group][ratio x q | k | v] (new decoder architecture), [q heads | k | v] (multi-query) or per-head [q k v]."""
+    name = type(block).__name__
+    if "Falcon" in name:
+        for m in block.modules():
+            if hasattr(m, "new_decoder_architecture") and hasattr(m, "multi_query"):
+                if m.new_decoder_architecture:
+                    return "falcon_grouped"
+                return "bigcodetype" if m.multi_query else "bloomtype"
+    for k in sorted(FUSED_QKV_TYPES, key=len, reverse=True):     # most specific class name first
+        if k in name:
+            return FUSED_QKV_TYPES[k]
+    return "glmtype"
+
+
+def _falcon_grouped(w: torch.Tensor, mp_size: int, rank: int, n_q: int, n_kv: int) -> torch.Tensor:
+    """[kv group][(n_q / n_kv) query heads | k | v][head_dim]: whole groups per rank."""
+    per = n_q // n_kv + 2
+    d = w.shape[0] // (n_kv * per)
+    g = w.reshape(n_kv, per * d, *w.shape[1:])
+    sizes = get_shard_size_list(n_kv, mp_size)
+    assert min(sizes) > 0, "grouped fused QKV needs at least one KV group per rank"
+    start = sum(sizes[:rank])
+    return g[start:start + sizes[rank]].reshape(-1, *w.shape[1:])
 
 
 def require_tp_fused_qkvw(name: str, mp_size: int) -> bool:
@@ -56,12 +84,18 @@ def prepare_tp_fused_qkvw(module, src: torch.Tensor, mp_size: int, gpu_index: in
     """Return rank ``gpu_index``'s slice of a fused QKV weight / bias of ``module``'s block type."""
     kind = None
     name = module if isinstance(module, str) else type(module).__name__
-    for k, v in FUSED_QKV_TYPES.items():
-        if k in name:
-            kind = v
-            break
+    if name in ("glmtype", "qwentype", "codegentype", "bloomtype", "phi3type", "bigcodetype", "falcon_grouped"):
+        kind = name
+    else:
+        for k in sorted(FUSED_QKV_TYPES, key=len, reverse=True):
+            if k in name:
+                kind = FUSED_QKV_TYPES[k]
+                break
     if kind is None:
         kind = "glmtype"
+    if kind == "falcon_grouped":
+        assert num_heads is not None and num_kv_heads is not None
+        return _falcon_grouped(src, mp_size, gpu_index, num_heads, num_kv_heads)
     if kind in ("glmtype", "qwentype", "codegentype"):
         return _glm_type(src, mp_size, gpu_index)
     if kind == "bloomtype":

@@ -72,3 +72,74 @@ def autotp_worker(rank, world):
             "types": [type(blk.self_attn.q_proj).__name__, type(blk.self_attn.o_proj).__name__, type(blk.mlp.down_proj).__name__,
                       type(model.lm_head).__name__], "heads": blk.self_attn.num_heads,
             "q_rows": blk.self_attn.q_proj.weight.shape[0], "o_cols": blk.self_attn.o_proj.weight.shape[1]}
+
+
+HF_AUTOTP_CASES = ("llama_gqa", "opt", "gpt2", "gptj", "gpt_neox", "bloom", "falcon_mqa", "falcon_new", "falcon_mha", "phi", "phi3",
+                   "qwen2", "mixtral", "gpt_neo")
+
+
+def _hf_tiny(kind):
+    import transformers as T
+    common = dict(hidden_size=64, num_hidden_layers=2, num_attention_heads=4, vocab_size=120, max_position_embeddings=128)
+    if kind == "llama_gqa":
+        return T.LlamaForCausalLM(T.LlamaConfig(intermediate_size=128, num_key_value_heads=2, **common))
+    if kind == "qwen2":
+        return T.Qwen2ForCausalLM(T.Qwen2Config(intermediate_size=128, num_key_value_heads=2, **common))
+    if kind == "opt":
+        return T.OPTForCausalLM(T.OPTConfig(ffn_dim=128, word_embed_proj_dim=64, **common))
+    if kind == "gpt2":
+        return T.GPT2LMHeadModel(T.GPT2Config(n_embd=64, n_layer=2, n_head=4, vocab_size=120, n_positions=128))
+    if kind == "gptj":
+        return T.GPTJForCausalLM(T.GPTJConfig(n_embd=64, n_layer=2, n_head=4, vocab_size=120, n_positions=128, rotary_dim=8))
+    if kind == "gpt_neox":
+        return T.GPTNeoXForCausalLM(T.GPTNeoXConfig(intermediate_size=128, **common))
+    if kind == "gpt_neo":
+        return T.GPTNeoForCausalLM(T.GPTNeoConfig(hidden_size=64, num_layers=2, num_heads=4, vocab_size=120, window_size=8,
+                                                  attention_types=[[["global", "local"], 1]], max_position_embeddings=128))
+    if kind == "bloom":
+        return T.BloomForCausalLM(T.BloomConfig(hidden_size=64, n_layer=2, n_head=4, vocab_size=120))
+    if kind == "falcon_mqa":
+        return T.FalconForCausalLM(T.FalconConfig(hidden_size=64, num_hidden_layers=2, num_attention_heads=4, vocab_size=120,
+                                                  multi_query=True, parallel_attn=True, new_decoder_architecture=False,
+                                                  alibi=False, bias=False))
+    if kind == "falcon_new":
+        return T.FalconForCausalLM(T.FalconConfig(hidden_size=64, num_hidden_layers=2, num_attention_heads=4, num_kv_heads=2,
+                                                  vocab_size=120, new_decoder_architecture=True, alibi=False, bias=False))
+    if kind == "falcon_mha":
+        return T.FalconForCausalLM(T.FalconConfig(hidden_size=64, num_hidden_layers=2, num_attention_heads=4, vocab_size=120,
+                                                  multi_query=False, parallel_attn=False, new_decoder_architecture=False,
+                                                  alibi=False, bias=True))
+    if kind == "phi3":
+        return T.Phi3ForCausalLM(T.Phi3Config(intermediate_size=128, num_key_value_heads=2, pad_token_id=0, **common))
+    if kind == "phi":
+        return T.PhiForCausalLM(T.PhiConfig(intermediate_size=128, partial_rotary_factor=0.5, **common))
+    if kind == "mixtral":
+        return T.MixtralForCausalLM(T.MixtralConfig(intermediate_size=96, num_key_value_heads=2, num_local_experts=4,
+                                                    num_experts_per_tok=2, sliding_window=None, **common))
+    raise KeyError(kind)
+
+
+def hf_autotp_worker(rank, world, kinds):
+    """AutoTP (no kernel injection) on real HuggingFace architectures: logits of the sharded model == unsharded logits."""
+    import hcache_deepspeed_b200 as ds
+    ds.init_distributed(dist_backend="gloo")
+    out = {}
+    for kind in kinds:
+        torch.manual_seed(0)
+        try:
+            model = _hf_tiny(kind).eval().float()
+        except Exception as e:  # config drift between transformers versions
+            out[kind] = f"skip: {type(e).__name__}: {e}"
+            continue
+        ids = torch.randint(1, 120, (2, 11))
+        with torch.no_grad():
+            want = model(ids).logits
+        try:
+            eng = ds.init_inference(model, dtype=torch.float32, tensor_parallel={"tp_size": world})
+            with torch.no_grad():
+                got = eng(ids).logits
+            out[kind] = float((got - want).abs().max())
+        except Exception as e:
+            import traceback
+            out[kind] = f"error: {type(e).__name__}: {e} | {traceback.format_exc().splitlines()[-3].strip()}"
+    return out

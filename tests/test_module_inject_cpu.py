@@ -62,3 +62,26 @@ def test_autotp_matches_unsharded(world):
         assert r["gems"] == ["mlp.down_proj", "self_attn.o_proj"]
         assert r["types"] == ["LinearLayer", "LinearAllreduce", "LinearAllreduce", "LmHeadLinearAllreduce"]
         assert r["heads"] == 4 // world and r["q_rows"] == 32 // world and r["o_cols"] == 32 // world
+
+
+def test_autotp_on_huggingface_architectures():
+    """AutoTP (no kernel injection) over two gloo ranks on fourteen real HuggingFace architectures: Conv1D projections
+    (GPT-2), every fused-QKV layout (per-head interleaved: BLOOM / GPT-NeoX / Falcon; [q | k | v]: GPT-2; multi-query and
+    grouped Falcon; Phi-3's GQA fused QKV + fused gate/up), ALiBi slopes per rank (BLOOM), attention modules that read head
+    counts from their config (Phi-3), MoE experts (Mixtral). Sharded logits == unsharded logits."""
+    pytest.importorskip("transformers")
+    from tests.autotp_helper import HF_AUTOTP_CASES, hf_autotp_worker
+    res = run_distributed(hf_autotp_worker, 2, list(HF_AUTOTP_CASES), timeout=600)
+    for r in res:
+        bad = {k: v for k, v in r.items() if not (isinstance(v, float) and v < 1e-4) and not str(v).startswith("skip")}
+        assert not bad, bad
+        assert sum(isinstance(v, float) for v in r.values()) >= 10
+
+
+def test_autotp_four_ranks_mha_mqa_and_gqa_limit():
+    pytest.importorskip("transformers")
+    from tests.autotp_helper import hf_autotp_worker
+    res = run_distributed(hf_autotp_worker, 4, ["bloom", "gpt2", "falcon_mqa", "llama_gqa"], timeout=600)
+    for r in res:
+        assert r["bloom"] < 1e-4 and r["gpt2"] < 1e-4 and r["falcon_mqa"] < 1e-4
+        assert "cannot be split over 4 ranks" in str(r["llama_gqa"])      # 2 KV heads: a clear error on every rank, no hang
