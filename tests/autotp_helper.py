@@ -143,3 +143,23 @@ def hf_autotp_worker(rank, world, kinds):
             import traceback
             out[kind] = f"error: {type(e).__name__}: {e} | {traceback.format_exc().splitlines()[-3].strip()}"
     return out
+
+
+def v1_inject_tp_worker(rank, world, kinds):
+    """``init_inference(replace_with_kernel_inject=True, tensor_parallel={tp_size: world})`` on real HF models: the stack
+    moves onto the ragged executor, sharded over the ranks; logits match the unsharded HF model and ``generate`` runs."""
+    import hcache_deepspeed_b200 as ds
+    ds.init_distributed(dist_backend="gloo")
+    out = {}
+    for kind in kinds:
+        torch.manual_seed(0)
+        model = _hf_tiny(kind).eval().float()
+        ids = torch.randint(1, 120, (2, 11))
+        with torch.no_grad():
+            want = model(ids).logits
+            want_gen = model.generate(ids, max_new_tokens=4, do_sample=False, pad_token_id=0)
+        eng = ds.init_inference(model, dtype=torch.float32, replace_with_kernel_inject=True, tensor_parallel={"tp_size": world})
+        got = eng(ids).logits
+        gen = eng.generate(ids, max_new_tokens=4, do_sample=False)
+        out[kind] = {"err": float((got - want).abs().max()), "injected": bool(eng.injected), "gen_equal": bool(torch.equal(gen, want_gen))}
+    return out

@@ -85,3 +85,12 @@ def test_autotp_four_ranks_mha_mqa_and_gqa_limit():
     for r in res:
         assert r["bloom"] < 1e-4 and r["gpt2"] < 1e-4 and r["falcon_mqa"] < 1e-4
         assert "cannot be split over 4 ranks" in str(r["llama_gqa"])      # 2 KV heads: a clear error on every rank, no hang
+
+
+def test_v1_kernel_inject_under_tensor_parallelism_hf_models():
+    pytest.importorskip("transformers")
+    from tests.autotp_helper import v1_inject_tp_worker
+    kinds = ["llama_gqa", "bloom", "gpt2", "falcon_mqa", "mixtral", "gpt_neo", "phi3"]
+    for r in run_distributed(v1_inject_tp_worker, 2, kinds, timeout=600):
+        for k in kinds:
+            assert r[k]["injected"] and r[k]["err"] < 1e-4 and r[k]["gen_equal"], (k, r[k])
