@@ -238,7 +238,35 @@ class Init:
 
         for cls in self._all_subclasses(torch.nn.Module):
             wrap(cls)
+        self._patch_hf_weight_init()
         return self
+
+    def _patch_hf_weight_init(self):
+        """HuggingFace models re-initialise every sub-module AFTER construction (``post_init`` -> ``_initialize_weights``),
+        i.e. after this context has already partitioned the parameters. Their initialisers would then write into empty
+        placeholders. While the context is active the per-module initialiser therefore runs with the module's own
+        parameters gathered; rank 0's values are broadcast and re-partitioned on the way out. (HF does the same from its side
+        for the ``deepspeed`` package; this is that hook for this one.)"""
+        import sys
+        self._hf_patch = None
+        mu = sys.modules.get("transformers.modeling_utils")
+        base = getattr(mu, "PreTrainedModel", None) if mu is not None else None
+        orig = getattr(base, "_initialize_weights", None) if base is not None else None
+        if orig is None or getattr(orig, "_ds_zero_wrapped", False):
+            return
+        import functools
+
+        @functools.wraps(orig)
+        def initialize(model, module, *a, **k):
+            own = [p for p in module.parameters(recurse=False) if is_zero_param(p)]
+            if not own or getattr(module, "_is_hf_initialized", False):
+                return orig(model, module, *a, **k)
+            with GatheredParameters(own, modifier_rank=0):
+                return orig(model, module, *a, **k)
+
+        initialize._ds_zero_wrapped = True
+        base._initialize_weights = initialize
+        self._hf_patch = (base, orig)
 
     def __exit__(self, *exc):
         if not self.enabled:
@@ -248,6 +276,10 @@ class Init:
             for cls, orig in self._wrapped:
                 cls.__init__ = orig
             self._wrapped = []
+            if getattr(self, "_hf_patch", None):
+                base, orig = self._hf_patch
+                base._initialize_weights = orig
+                self._hf_patch = None
         return False
 
 

@@ -281,3 +281,28 @@ def zero3_frozen_worker(rank, world, ckpt_dir):
     if rank == 0:
         out["fp32_from_shards"] = {k: v.clone() for k, v in get_fp32_state_dict_from_zero_checkpoint(ckpt_dir, tag="z3").items()}
     return out
+
+
+def zero_init_hf_worker(rank, world):
+    """``zero.Init`` around a HuggingFace constructor: HF re-initialises every module after construction; the values must
+    land in the partitions (ref: HF's deepspeed integration gathers params inside ``_init_weights``)."""
+    import transformers as T
+    import hcache_deepspeed_b200 as ds
+    from hcache_deepspeed_b200.runtime.zero import GatheredParameters
+    from hcache_deepspeed_b200.runtime.zero.partition_parameters import is_zero_param
+    ds.init_distributed(dist_backend="gloo")
+    cfg = T.GPT2Config(n_embd=64, n_layer=2, n_head=4, vocab_size=120, n_positions=128)
+    torch.manual_seed(0)
+    plain = T.GPT2LMHeadModel(cfg)
+    torch.manual_seed(0 if rank == 0 else 77)          # only rank 0's initialisation counts
+    with ds.zero.Init(config_dict_or_path={"train_micro_batch_size_per_gpu": 1, "zero_optimization": {"stage": 3}}):
+        model = T.GPT2LMHeadModel(cfg)
+    assert T.modeling_utils.PreTrainedModel._initialize_weights.__dict__.get("_ds_zero_wrapped") is None     # patch removed
+    worst, n_zero = 0.0, 0
+    for (n, p), (_, q) in zip(model.named_parameters(), plain.named_parameters()):
+        n_zero += int(is_zero_param(p))
+        with GatheredParameters([p]):
+            worst = max(worst, float((p.data.float() - q.data.float()).abs().max()))
+    with GatheredParameters([model.transformer.wte.weight]):
+        std = float(model.transformer.wte.weight.data.float().std())
+    return {"worst": worst, "n_zero": n_zero, "wte_std": std}

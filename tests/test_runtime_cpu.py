@@ -438,3 +438,11 @@ def test_hybrid_engine_lora_generate_tracks_training(stage):
     assert engine._inference_engine is None
     engine.retake_inference_cache()
     assert engine._inference_engine is not None
+
+
+def test_zero_init_around_huggingface_constructor_2ranks():
+    pytest.importorskip("transformers")
+    from tests.runtime_helper import zero_init_hf_worker
+    for r in run_distributed(zero_init_hf_worker, 2):
+        assert r["n_zero"] > 10 and r["worst"] == 0.0            # every rank holds rank 0's HF initialisation
+        assert 0.015 < r["wte_std"] < 0.025                      # initializer_range 0.02, not nn.Embedding's N(0, 1)
