@@ -164,6 +164,7 @@ class Init:
     """Context manager: modules constructed inside are partitioned as they are created (``module=...`` converts an
     existing one). ``remote_device`` ('cpu') keeps slices in host memory, ``pin_memory`` pins them."""
     _active = 0
+    _suspended = 0      # > 0 while a HuggingFace from_pretrained runs inside the context (see _patch_hf_weight_init)
 
     def __init__(self, module: Optional[torch.nn.Module] = None, data_parallel_group=None, mem_efficient_linear: bool = True,
                  remote_device: Optional[str] = None, pin_memory: bool = False, config_dict_or_path=None, config=None,
@@ -228,7 +229,7 @@ class Init:
                     orig(mod, *a, **k)
                 finally:
                     mod._ds_init_depth -= 1
-                if mod._ds_init_depth == 0 and Init._active > 0:
+                if mod._ds_init_depth == 0 and Init._active > 0 and Init._suspended == 0:
                     for p in mod.parameters(recurse=False):
                         _convert(p, ctx.group, ctx.remote_device, ctx.pin_memory, ctx.persistence_threshold, ctx.dtype)
 
@@ -266,7 +267,26 @@ class Init:
 
         initialize._ds_zero_wrapped = True
         base._initialize_weights = initialize
-        self._hf_patch = (base, orig)
+        # ``from_pretrained`` builds the model on the meta device and then loads tensors by shape, which cannot work on
+        # partitioned placeholders: it runs with partitioning suspended and the finished model is partitioned in one go
+        # (every rank reads the checkpoint; peak memory is one full copy per rank, as without this context)
+        orig_fp = base.__dict__["from_pretrained"]
+        fp_func = orig_fp.__func__ if isinstance(orig_fp, classmethod) else orig_fp
+        ctx = self
+
+        @functools.wraps(fp_func)
+        def from_pretrained(cls, *a, **k):
+            Init._suspended += 1
+            try:
+                model = fp_func(cls, *a, **k)
+            finally:
+                Init._suspended -= 1
+            if Init._suspended == 0 and Init._active > 0:
+                ctx._convert_module(model)
+            return model
+
+        base.from_pretrained = classmethod(from_pretrained)
+        self._hf_patch = (base, orig, orig_fp)
 
     def __exit__(self, *exc):
         if not self.enabled:
@@ -277,8 +297,9 @@ class Init:
                 cls.__init__ = orig
             self._wrapped = []
             if getattr(self, "_hf_patch", None):
-                base, orig = self._hf_patch
+                base, orig, orig_fp = self._hf_patch
                 base._initialize_weights = orig
+                base.from_pretrained = orig_fp
                 self._hf_patch = None
         return False
 

@@ -305,4 +305,29 @@ def zero_init_hf_worker(rank, world):
             worst = max(worst, float((p.data.float() - q.data.float()).abs().max()))
     with GatheredParameters([model.transformer.wte.weight]):
         std = float(model.transformer.wte.weight.data.float().std())
-    return {"worst": worst, "n_zero": n_zero, "wte_std": std}
+    out = {"worst": worst, "n_zero": n_zero, "wte_std": std}
+    # from_pretrained inside the context: loads with partitioning suspended, then the whole model is partitioned
+    import os
+    import tempfile
+    d = os.path.join(tempfile.gettempdir(), f"hds_zinit_{os.getppid()}")
+    if rank == 0:
+        plain.save_pretrained(d)
+    torch.distributed.barrier()
+    with ds.zero.Init(config_dict_or_path={"train_micro_batch_size_per_gpu": 1, "zero_optimization": {"stage": 3}}):
+        loaded = T.AutoModelForCausalLM.from_pretrained(d)
+    worst = 0.0
+    for (n, p), (_, q) in zip(loaded.named_parameters(), plain.named_parameters()):
+        assert is_zero_param(p), n
+        with GatheredParameters([p]):
+            worst = max(worst, float((p.data.float() - q.data.float()).abs().max()))
+    engine, _, _, _ = ds.initialize(model=loaded, config={"train_micro_batch_size_per_gpu": 1, "zero_optimization": {"stage": 3},
+                                                          "optimizer": {"type": "AdamW", "params": {"lr": 1e-3}}})
+    ids = torch.randint(1, 120, (1, 9))
+    with torch.no_grad():
+        out["pretrained_logits"] = float((engine(input_ids=ids).logits - plain(ids).logits).abs().max())
+    out["pretrained_worst"] = worst
+    torch.distributed.barrier()
+    if rank == 0:
+        import shutil
+        shutil.rmtree(d, ignore_errors=True)
+    return out

@@ -446,3 +446,4 @@ def test_zero_init_around_huggingface_constructor_2ranks():
     for r in run_distributed(zero_init_hf_worker, 2):
         assert r["n_zero"] > 10 and r["worst"] == 0.0            # every rank holds rank 0's HF initialisation
         assert 0.015 < r["wte_std"] < 0.025                      # initializer_range 0.02, not nn.Embedding's N(0, 1)
+        assert r["pretrained_worst"] == 0.0 and r["pretrained_logits"] < 1e-5
