@@ -323,6 +323,8 @@ def zero_init_hf_worker(rank, world):
     engine, _, _, _ = ds.initialize(model=loaded, config={"train_micro_batch_size_per_gpu": 1, "zero_optimization": {"stage": 3},
                                                           "optimizer": {"type": "AdamW", "params": {"lr": 1e-3}}})
     ids = torch.randint(1, 120, (1, 9))
+    engine.eval()           # GPT-2 has dropout
+    plain.eval()
     with torch.no_grad():
         out["pretrained_logits"] = float((engine(input_ids=ids).logits - plain(ids).logits).abs().max())
     out["pretrained_worst"] = worst
