@@ -180,6 +180,12 @@ def main(args=None):
             subprocess.check_output(["ssh", first, "hostname -I"]).decode().split()[0]
     world_info = encode_world_info(active)
     env = os.environ.copy()
+    # a source checkout that is not installed: the per-node launcher and the ranks import the package through PYTHONPATH
+    # (exported to remote nodes too, "PYTHON" is in EXPORT_ENVS)
+    pkg_root = os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+    paths = [p for p in env.get("PYTHONPATH", "").split(os.pathsep) if p]
+    if pkg_root not in paths:
+        env["PYTHONPATH"] = os.pathsep.join([pkg_root] + paths)
     if not multi_node:
         cmd = build_launch_cmd(args, world_info, node_rank="0")
     else:

@@ -21,7 +21,8 @@ CSRC = OPS_DIR / "csrc"
 HOST_SRC = OPS_DIR / "csrc_host"
 LIB_DIR = OPS_DIR / "lib"
 OBJ_DIR = OPS_DIR / "lib" / "obj"
-REPO_INCLUDE = OPS_DIR.parent.parent / "include"
+# public headers: <repo>/include in a source checkout, <package>/include in an installed tree (setup.py copies them there)
+REPO_INCLUDE = OPS_DIR.parent / "include" if (OPS_DIR.parent / "include" / "hds_b200.h").exists() else OPS_DIR.parent.parent / "include"
 
 CUDA_LIB = LIB_DIR / "libhds_b200.so"
 HOST_LIB = LIB_DIR / "libhds_host.so"

@@ -778,3 +778,69 @@ def test_op_builder_probes_jit_and_dependency_tables(tmp_path, monkeypatch):
     assert q2.is_compatible() and any("nvcc not found" in w for w in q2.error_log)
     with pytest.raises(OpBuildError, match="nvcc not found"):
         q2.jit_build(verbose=False)
+
+
+def test_launcher_end_to_end_from_another_directory(tmp_path):
+    """``bin/hds`` from a source checkout that is not installed, started in an unrelated directory: two local ranks come
+    up (hostfile + --include), see their LOCAL_RANK, all-reduce over gloo; a failing rank's exit code becomes the
+    launcher's and its siblings are stopped (ref: launcher/runner.py + launch.py)."""
+    import sys
+    import time
+    repo = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    probe = tmp_path / "probe.py"
+    probe.write_text(
+        "import argparse, os, torch\n"
+        "import hcache_deepspeed_b200 as ds\n"
+        "p = argparse.ArgumentParser(); p.add_argument('--local_rank', type=int, default=-1); p.add_argument('--tag'); a = p.parse_args()\n"
+        "ds.init_distributed(dist_backend='gloo')\n"
+        "t = torch.ones(1) * (ds.comm.get_rank() + 1); ds.comm.all_reduce(t)\n"
+        "print(f'RESULT {ds.comm.get_rank()} {ds.comm.get_world_size()} {a.local_rank} {os.environ[\"LOCAL_RANK\"]} {float(t)} {a.tag}', flush=True)\n")
+    (tmp_path / "hostfile").write_text("localhost slots=4\n")
+    env = {k: v for k, v in os.environ.items() if k not in ("PYTHONPATH", "RANK", "WORLD_SIZE", "LOCAL_RANK", "MASTER_ADDR", "MASTER_PORT")}
+    env["CUDA_VISIBLE_DEVICES"] = ""
+    from tests.dist_utils import _free_port
+    out = subprocess.run([sys.executable, os.path.join(repo, "bin", "hds"), "-H", str(tmp_path / "hostfile"), "--include", "localhost:1,3",
+                          "--master_port", str(_free_port()), str(probe), "--tag", "hello"], cwd=str(tmp_path), env=env,
+                         stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True, timeout=300)
+    lines = sorted(l for l in out.stdout.splitlines() if l.startswith("RESULT"))
+    assert out.returncode == 0 and lines == ["RESULT 0 2 0 0 3.0 hello", "RESULT 1 2 1 1 3.0 hello"], out.stdout[-2000:]
+    bad = tmp_path / "bad.py"
+    bad.write_text("import os, sys, time\nif os.environ['RANK'] == '1':\n    sys.exit(7)\ntime.sleep(120)\n")
+    t0 = time.time()
+    out = subprocess.run([sys.executable, os.path.join(repo, "bin", "hds"), "--num_gpus", "2", "--master_port", str(_free_port()), str(bad)],
+                         cwd=str(tmp_path), env=env, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True, timeout=300)
+    assert out.returncode == 7 and time.time() - t0 < 90, (out.returncode, out.stdout[-1500:])
+
+
+def test_pip_install_into_target_and_use_from_there(tmp_path):
+    """``pip install --no-build-isolation .`` (setup.py: builds the in-tree libraries, ships them + the CUDA / C++ sources +
+    the public headers, installs the CLI scripts); the installed copy works from an unrelated directory, including a JIT
+    build of one op against the packaged headers."""
+    import shutil
+    import sys
+    repo = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    src = tmp_path / "src"                       # build from a copy: pip writes build/ and egg-info next to setup.py
+    shutil.copytree(repo, src, ignore=shutil.ignore_patterns(".git", "gpurun_out", "baseline", "profiles", "tests", "__pycache__",
+                                                             "obj", "jit", "build", "*.egg-info"))
+    target = tmp_path / "site"
+    res = subprocess.run([sys.executable, "-m", "pip", "install", "--no-index", "--no-build-isolation", "--no-deps", "--target",
+                          str(target), str(src)], stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True, timeout=1200)
+    assert res.returncode == 0, res.stdout[-3000:]
+    pkg = target / "hcache_deepspeed_b200"
+    assert (pkg / "ops" / "lib" / "libhds_host.so").exists() and (pkg / "ops" / "lib" / "libhds_b200.so").exists()
+    assert (pkg / "include" / "hds_b200.h").exists() and (pkg / "ops" / "csrc" / "gemm.cu").exists()
+    assert (target / "bin" / "hds").exists() and (target / "bin" / "hds_report").exists()
+    code = ("import os, torch, hcache_deepspeed_b200 as ds\n"
+            "from hcache_deepspeed_b200.ops import build\n"
+            "from hcache_deepspeed_b200.ops.op_builder import ALL_OPS, ShareMemCommBuilder\n"
+            "assert ds.__file__.startswith(os.environ['HDS_T']), ds.__file__\n"
+            "assert str(build.REPO_INCLUDE).startswith(os.environ['HDS_T'])\n"
+            "assert all(b.installed() for b in ALL_OPS.values())\n"
+            "os.environ['HDS_FORCE_JIT'] = '1'\n"
+            "assert hasattr(ShareMemCommBuilder().load(verbose=False), 'hds_shm_barrier')\n"
+            "print('INSTALLED-OK')\n")
+    env = {k: v for k, v in os.environ.items() if k != "PYTHONPATH"}
+    env.update(PYTHONPATH=str(target), HDS_T=str(target), HDS_JIT_DIR=str(tmp_path / "jit"))
+    out = subprocess.run([sys.executable, "-c", code], cwd=str(tmp_path), env=env, stdout=subprocess.PIPE, stderr=subprocess.STDOUT,
+                         text=True, timeout=600)
+    assert "INSTALLED-OK" in out.stdout, out.stdout[-3000:]
