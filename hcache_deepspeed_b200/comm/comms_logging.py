@@ -50,8 +50,15 @@ class CommsLogger:
 
     def configure(self, comms_config=None, enabled=None, prof_all=None, prof_ops=None, verbose=None, debug=None):
         if comms_config is not None:
-            self.enabled = getattr(comms_config, "comms_logger_enabled", self.enabled)
+            # either the wrapper (``DeepSpeedCommsConfig``: comms_logger_enabled + comms_logger) or the ``comms_logger`` block
+            # itself (``CommsLoggerConfig``, what the training config carries)
             cl = getattr(comms_config, "comms_logger", None)
+            if cl is None and hasattr(comms_config, "prof_all"):
+                cl = comms_config
+                self.enabled = bool(cl.enabled)
+            else:
+                self.enabled = bool(getattr(comms_config, "comms_logger_enabled", self.enabled)) and \
+                    bool(getattr(cl, "enabled", True))
             if cl is not None:
                 self.verbose, self.debug = cl.verbose, cl.debug
                 self.prof_ops, self.prof_all = cl.prof_ops, cl.prof_all

@@ -844,3 +844,30 @@ def test_pip_install_into_target_and_use_from_there(tmp_path):
     out = subprocess.run([sys.executable, "-c", code], cwd=str(tmp_path), env=env, stdout=subprocess.PIPE, stderr=subprocess.STDOUT,
                          text=True, timeout=600)
     assert "INSTALLED-OK" in out.stdout, out.stdout[-3000:]
+
+
+def test_comms_logger_enabled_from_training_config():
+    """``"comms_logger": {"enabled": true}`` in the training config must switch the logger on (the engine passes its config
+    object to ``comm.configure``); both config shapes are understood."""
+    from hcache_deepspeed_b200.comm import comm as C
+    from hcache_deepspeed_b200.comm.config import DeepSpeedCommsConfig
+    from hcache_deepspeed_b200.runtime.config import DeepSpeedConfig
+    saved = (C.comms_logger.enabled, C.comms_logger.prof_all, list(C.comms_logger.prof_ops), C.comms_logger.verbose)
+    try:
+        cfg = DeepSpeedConfig({"train_batch_size": 1, "comms_logger": {"enabled": True, "prof_all": False, "prof_ops": ["all_reduce"]}})
+        C.comms_logger.enabled = False
+        C.configure(cfg)
+        assert C.comms_logger.enabled and not C.comms_logger.prof_all and C.comms_logger.prof_ops == ["all_reduce"]
+        C.configure(DeepSpeedConfig({"train_batch_size": 1, "comms_logger": {"enabled": False}}))
+        assert not C.comms_logger.enabled
+        wrapper = types.SimpleNamespace(comms_config=DeepSpeedCommsConfig({"comms_logger": {"enabled": True, "verbose": True}}))
+        C.configure(wrapper)
+        assert C.comms_logger.enabled and C.comms_logger.verbose
+        # a timed op is recorded once the logger is on (single process: the size / latency bookkeeping is what is checked)
+        C.comms_logger.comms_dict.clear()
+        C.comms_logger.configure(enabled=True, prof_all=True)
+        C.comms_logger.append("all_reduce", "all_reduce", 1.5, 4096, 2)
+        assert "all_reduce" in C.comms_logger.log_all(print_log=False)
+    finally:
+        C.comms_logger.enabled, C.comms_logger.prof_all, C.comms_logger.prof_ops, C.comms_logger.verbose = saved
+        C.comms_logger.comms_dict.clear()
