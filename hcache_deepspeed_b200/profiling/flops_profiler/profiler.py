@@ -82,13 +82,87 @@ def _embedding_flops(inp, weight, *_, **__):
     return 0, 0
 
 
+def _einsum_flops(equation, *operands):
+    """MACs of an einsum = product of the sizes of every index that appears (each output element sums over the
+    contracted indices)."""
+    if len(operands) == 1 and isinstance(operands[0], (list, tuple)):
+        operands = tuple(operands[0])
+    lhs = equation.replace(" ", "").split("->")[0].split(",")
+    sizes = {}
+    for term, op in zip(lhs, operands):
+        term = term.replace("...", "")
+        for ch, n in zip(term[::-1], tuple(op.shape)[::-1]):
+            sizes[ch] = int(n)
+    macs = _prod(sizes.values())
+    return 2 * macs, macs
+
+
+def _baddbmm_flops(inp, a, b, *_, **__):
+    macs = a.shape[0] * a.shape[1] * a.shape[2] * b.shape[-1]
+    return 2 * macs + inp.numel(), macs
+
+
+def _norm_flops(mult: int):
+    def fn(inp, *_, **__):
+        return mult * inp.numel(), 0
+    return fn
+
+
+def _pool_flops(inp, *_, **__):
+    return inp.numel(), 0
+
+
+def _interpolate_flops(inp, size=None, scale_factor=None, *_, **__):
+    n = inp.numel()
+    if size is not None:
+        out = _prod(size) if isinstance(size, (tuple, list)) else int(size) ** max(1, inp.dim() - 2)
+        n = _prod(inp.shape[:2]) * out
+    elif scale_factor is not None:
+        sf = scale_factor if isinstance(scale_factor, (tuple, list)) else [scale_factor] * max(1, inp.dim() - 2)
+        n = int(inp.numel() * _prod([float(x) for x in sf]) if all(float(x).is_integer() for x in sf) else inp.numel())
+    return n, 0
+
+
+def _conv_transpose_flops(inp, weight, bias=None, stride=1, padding=0, output_padding=0, groups=1, dilation=1):
+    # every input element is multiplied with its kernel slice: in_elems * (out_channels / groups) * kernel_volume
+    macs = inp.numel() * (weight.shape[1]) * _prod(weight.shape[2:])
+    return 2 * macs + (0 if bias is None else macs // max(1, _prod(weight.shape[2:]))), macs
+
+
+def _tensor_binary(a, b=None, *_, **__):
+    n = a.numel() if hasattr(a, "numel") else 0
+    if hasattr(b, "numel"):
+        n = max(n, b.numel())
+    return n, 0
+
+
 FUNCTIONAL_PATCHES = {
     (F, "linear"): _linear_flops, (F, "conv1d"): _conv_flops, (F, "conv2d"): _conv_flops, (F, "conv3d"): _conv_flops,
-    (F, "relu"): _elementwise(1), (F, "gelu"): _elementwise(8), (F, "silu"): _elementwise(4), (F, "softmax"): _elementwise(5),
-    (F, "layer_norm"): _elementwise(5), (F, "embedding"): _embedding_flops,
+    (F, "conv_transpose1d"): _conv_transpose_flops, (F, "conv_transpose2d"): _conv_transpose_flops,
+    (F, "conv_transpose3d"): _conv_transpose_flops,
+    (F, "relu"): _elementwise(1), (F, "relu6"): _elementwise(1), (F, "leaky_relu"): _elementwise(1), (F, "prelu"): _elementwise(1),
+    (F, "elu"): _elementwise(4), (F, "gelu"): _elementwise(8), (F, "silu"): _elementwise(4), (F, "sigmoid"): _elementwise(4),
+    (F, "tanh"): _elementwise(4), (F, "softmax"): _elementwise(5), (F, "log_softmax"): _elementwise(6),
+    (F, "layer_norm"): _norm_flops(5), (F, "group_norm"): _norm_flops(5), (F, "batch_norm"): _norm_flops(2),
+    (F, "instance_norm"): _norm_flops(5), (F, "rms_norm"): _norm_flops(4),
+    (F, "avg_pool1d"): _pool_flops, (F, "avg_pool2d"): _pool_flops, (F, "avg_pool3d"): _pool_flops,
+    (F, "max_pool1d"): _pool_flops, (F, "max_pool2d"): _pool_flops, (F, "max_pool3d"): _pool_flops,
+    (F, "adaptive_avg_pool1d"): _pool_flops, (F, "adaptive_avg_pool2d"): _pool_flops, (F, "adaptive_avg_pool3d"): _pool_flops,
+    (F, "adaptive_max_pool1d"): _pool_flops, (F, "adaptive_max_pool2d"): _pool_flops, (F, "adaptive_max_pool3d"): _pool_flops,
+    (F, "interpolate"): _interpolate_flops, (F, "upsample"): _interpolate_flops,
+    (F, "embedding"): _embedding_flops,
     (F, "scaled_dot_product_attention"): _sdpa_flops,
-    (torch, "matmul"): _matmul_flops, (torch, "bmm"): _bmm_flops, (torch, "addmm"): _addmm_flops,
-    (torch.Tensor, "matmul"): _matmul_flops, (torch.Tensor, "__matmul__"): _matmul_flops,
+    (torch, "matmul"): _matmul_flops, (torch, "mm"): _matmul_flops, (torch, "bmm"): _bmm_flops, (torch, "addmm"): _addmm_flops,
+    (torch, "baddbmm"): _baddbmm_flops, (torch, "einsum"): _einsum_flops,
+    (torch.Tensor, "matmul"): _matmul_flops, (torch.Tensor, "__matmul__"): _matmul_flops, (torch.Tensor, "mm"): _matmul_flops,
+    (torch.Tensor, "bmm"): _bmm_flops, (torch.Tensor, "baddbmm"): _baddbmm_flops,
+}
+# element-wise tensor arithmetic is counted only on request (``FlopsProfiler(count_elementwise=True)``): it is a rounding
+# error next to the GEMMs and wrapping ``Tensor.__add__`` slows every profiled step down
+ELEMENTWISE_PATCHES = {
+    (torch, "add"): _tensor_binary, (torch, "mul"): _tensor_binary, (torch, "sub"): _tensor_binary, (torch, "div"): _tensor_binary,
+    (torch.Tensor, "__add__"): _tensor_binary, (torch.Tensor, "__mul__"): _tensor_binary, (torch.Tensor, "__sub__"): _tensor_binary,
+    (torch.Tensor, "__truediv__"): _tensor_binary,
 }
 
 
@@ -104,8 +178,11 @@ def _wrap(orig, counter):
     return wrapped
 
 
-def _patch_all():
-    for (owner, name), counter in FUNCTIONAL_PATCHES.items():
+def _patch_all(elementwise: bool = False):
+    table = dict(FUNCTIONAL_PATCHES)
+    if elementwise:
+        table.update(ELEMENTWISE_PATCHES)
+    for (owner, name), counter in table.items():
         orig = getattr(owner, name, None)
         if orig is None or getattr(orig, "__wrapped_by_flops_profiler__", False):
             continue
@@ -131,17 +208,19 @@ class FlopsProfiler:
     """``prof = FlopsProfiler(model); prof.start_profile(); model(x); prof.stop_profile();
     prof.get_total_flops(); prof.print_model_profile(); prof.end_profile()``"""
 
-    def __init__(self, model: torch.nn.Module, ds_engine=None, recompute_fwd_factor: float = 0.0):
+    def __init__(self, model: torch.nn.Module, ds_engine=None, recompute_fwd_factor: float = 0.0,
+                 count_elementwise: bool = False):
         self.model = model
         self.ds_engine = ds_engine
         self.recompute_fwd_factor = recompute_fwd_factor
+        self.count_elementwise = count_elementwise
         self.started = False
         self.func_patched = False
         self._handles = []
 
     def start_profile(self, ignore_list=None):
         self.reset_profile()
-        _patch_all()
+        _patch_all(self.count_elementwise)
         self.func_patched = True
 
         def pre(module, inp):
@@ -206,30 +285,127 @@ class FlopsProfiler:
         return f"{v * 1e3:.2f} ms" if as_string else v
 
     def get_total_params(self, as_string: bool = False):
-        v = sum(p.numel() for p in self.model.parameters())
+        v = self._total_params_of(self.model)          # ZeRO-3 placeholders count with their full size
         return number_to_string(v) if as_string else v
+
+    # ---- aggregation ------------------------------------------------------------------------------------------------
+    def _total_params_of(self, module) -> int:
+        return sum(p.numel() if not hasattr(p, "ds_numel") else p.ds_numel for p in module.parameters())
+
+    def print_model_aggregated_profile(self, module_depth: int = -1, top_modules: int = 1) -> List[str]:
+        """Top ``top_modules`` module classes per depth by parameters, MACs and forward latency (ref: profiler.py
+        print_model_aggregated_profile)."""
+        info: Dict[int, Dict[str, List[float]]] = {}
+
+        def walk(module, depth):
+            row = info.setdefault(depth, {}).setdefault(type(module).__name__, [0, 0, 0.0])
+            row[0] += self._total_params_of(module)
+            row[1] += module.__macs__
+            row[2] += module.__duration__
+            for c in module.children():
+                walk(c, depth + 1)
+
+        walk(self.model, 0)
+        depth = max(info) if module_depth < 0 else min(module_depth, max(info))
+        lines = [f"Top {top_modules} modules in terms of params, MACs or fwd latency at different model depths:"]
+        for d in range(depth + 1):
+            n = min(top_modules, len(info[d]))
+            top = lambda k: {name: v[k] for name, v in sorted(info[d].items(), key=lambda kv: kv[1][k], reverse=True)[:n]}
+            lines.append(f"depth {d}:")
+            lines.append("    params      - " + str({k: number_to_string(v).strip() for k, v in top(0).items()}))
+            lines.append("    MACs        - " + str({k: number_to_string(v).strip() + "MACs" for k, v in top(1).items()}))
+            lines.append("    fwd latency - " + str({k: f"{v * 1e3:.2f} ms" for k, v in top(2).items()}))
+        return lines
+
+    def _engine_summary(self, fwd_s: float) -> List[str]:
+        """The training-run header of the reference's report: parallel layout, batch size, fwd / bwd / step latency
+        (bwd and step need ``wall_clock_breakdown``), achieved FLOPS per GPU and samples per second."""
+        e = self.ds_engine
+        if e is None:
+            return []
+        flops = self.get_total_flops()
+        lines = [f"world size:                                                   {getattr(e, 'world_size', 1)}",
+                 f"data parallel size:                                           {getattr(e, 'dp_world_size', 1)}",
+                 f"model parallel size:                                          {getattr(e, 'mp_world_size', 1)}",
+                 f"batch size per GPU:                                           {e.train_micro_batch_size_per_gpu()}"]
+        bwd_s = step_s = 0.0
+        timers = getattr(e, "timers", None)
+        try:
+            from ...runtime.engine import BACKWARD_GLOBAL_TIMER, STEP_GLOBAL_TIMER
+            if timers is not None and hasattr(timers, "has_timer") and timers.has_timer(BACKWARD_GLOBAL_TIMER):
+                bwd_s = timers(BACKWARD_GLOBAL_TIMER).elapsed(reset=False) / 1e3
+                step_s = timers(STEP_GLOBAL_TIMER).elapsed(reset=False) / 1e3 if timers.has_timer(STEP_GLOBAL_TIMER) else 0.0
+        except Exception:
+            pass
+        factor = 2.0 + self.recompute_fwd_factor           # backward = 2 x forward (+ the recomputed share of the forward)
+        lines.append(f"fwd flops per GPU:                                            {number_to_string(flops)}FLOPs")
+        lines.append(f"fwd flops of model = fwd flops per GPU * mp_size:             "
+                     f"{number_to_string(flops * getattr(e, 'mp_world_size', 1))}FLOPs")
+        lines.append(f"fwd latency:                                                  {fwd_s * 1e3:.2f} ms")
+        if fwd_s > 0:
+            lines.append(f"fwd FLOPS per GPU = fwd flops per GPU / fwd latency:          {number_to_string(flops / fwd_s)}FLOPS")
+        if bwd_s > 0:
+            lines.append(f"bwd latency:                                                  {bwd_s * 1e3:.2f} ms")
+            lines.append(f"bwd FLOPS per GPU = {factor:g} * fwd flops per GPU / bwd latency:    "
+                         f"{number_to_string(factor * flops / bwd_s)}FLOPS")
+            lines.append(f"fwd+bwd FLOPS per GPU:                                        "
+                         f"{number_to_string((1 + factor) * flops / (fwd_s + bwd_s))}FLOPS")
+        if step_s > 0:
+            lines.append(f"step latency:                                                 {step_s * 1e3:.2f} ms")
+        it = fwd_s + bwd_s + step_s
+        if it > 0:
+            lines.append(f"iter latency:                                                 {it * 1e3:.2f} ms")
+            if bwd_s > 0:
+                lines.append(f"FLOPS per GPU = {1 + factor:g} * fwd flops per GPU / iter latency:       "
+                             f"{number_to_string((1 + factor) * flops / it)}FLOPS")
+                lines.append(f"samples/second:                                               "
+                             f"{e.train_micro_batch_size_per_gpu() * getattr(e, 'dp_world_size', 1) / it:.2f}")
+        return lines
 
     def print_model_profile(self, profile_step: int = 1, module_depth: int = -1, top_modules: int = 1, detailed: bool = True,
                             output_file: Optional[str] = None):
+        """Summary, per-depth top modules and (``detailed``) the module tree with each module's share of parameters, MACs
+        and forward latency plus its achieved FLOPS (ref: profiler.py print_model_profile)."""
+        dur = self.get_total_duration()
+        total_params = self._total_params_of(self.model)
+        total_macs = max(1, self.get_total_macs())
         lines = ["-------------------------- Flops Profiler --------------------------",
                  f"Profile Summary at step {profile_step}:",
-                 f"params:               {self.get_total_params(True)}",
-                 f"fwd MACs:             {self.get_total_macs(True)}",
-                 f"fwd flops:            {self.get_total_flops(True)}",
-                 f"fwd latency:          {self.get_total_duration(True)}"]
-        dur = self.get_total_duration()
+                 "Notations: data parallel size (dp_size), model parallel size(mp_size), number of parameters (params), "
+                 "number of multiply-accumulate operations(MACs), number of floating-point operations (flops), "
+                 "floating-point operations per second (FLOPS), fwd latency (forward propagation latency), "
+                 "bwd latency (backward propagation latency), step (weights update latency), iter latency (sum of fwd, bwd and step latency)",
+                 ""]
+        lines += self._engine_summary(dur)
+        lines += [f"params:               {number_to_string(total_params)}",
+                  f"fwd MACs:             {self.get_total_macs(True)}",
+                  f"fwd flops:            {self.get_total_flops(True)}",
+                  f"fwd latency:          {self.get_total_duration(True)}"]
         if dur > 0:
             lines.append(f"fwd FLOPS:            {number_to_string(self.get_total_flops() / dur)}FLOPS")
+        lines += ["", "----------------------------- Aggregated Profile per GPU -----------------------------"]
+        lines += self.print_model_aggregated_profile(module_depth=module_depth, top_modules=top_modules)
         if detailed:
-            lines.append("")
+            lines += ["", "------------------------------ Detailed Profile per GPU ------------------------------",
+                      "Each module profile is listed after its name in the following order:",
+                      "params, percentage of total params, MACs, percentage of total MACs, fwd latency, percentage of total fwd "
+                      "latency, fwd FLOPS", ""]
+
             def walk(module, name, depth):
                 if module_depth >= 0 and depth > module_depth:
                     return
-                lines.append("  " * depth + f"{name or type(module).__name__}: {number_to_string(module.__params__)}params, "
-                             f"{number_to_string(module.__macs__)}MACs, {module.__duration__ * 1e3:.2f} ms")
+                p = self._total_params_of(module)
+                d = module.__duration__
+                fl = f"{number_to_string(module.__flops__ / d)}FLOPS" if d > 0 else "0 FLOPS"
+                lines.append("  " * depth + f"({name}): {type(module).__name__}({number_to_string(p).strip()}, "
+                             f"{100.0 * p / max(1, total_params):.2f}% Params, {number_to_string(module.__macs__)}MACs, "
+                             f"{100.0 * module.__macs__ / total_macs:.2f}% MACs, {d * 1e3:.2f} ms, "
+                             f"{100.0 * d / dur if dur > 0 else 0.0:.2f}% latency, {fl})")
                 for n, c in module.named_children():
                     walk(c, n, depth + 1)
+
             walk(self.model, type(self.model).__name__, 0)
+        lines.append("------------------------------------------------------------------------------")
         text = "\n".join(lines)
         if output_file:
             with open(output_file, "w") as f:

@@ -132,7 +132,8 @@ class DeepSpeedEngine(torch.nn.Module):
         self.flops_profiler = None
         if self._config.flops_profiler_config.enabled:
             from ..profiling.flops_profiler.profiler import FlopsProfiler
-            self.flops_profiler = FlopsProfiler(self.module, self)
+            self.flops_profiler = FlopsProfiler(self.module, self,
+                                                recompute_fwd_factor=self._config.flops_profiler_config.recompute_fwd_factor)
         self.progressive_layer_drop = None
         if self._config.pld_enabled:
             from .progressive_layer_drop import ProgressiveLayerDrop
@@ -487,13 +488,8 @@ class DeepSpeedEngine(torch.nn.Module):
         loss = self.module(*inputs, **kwargs)
         self.timers(FORWARD_MICRO_TIMER).stop()
         self.timers(FORWARD_GLOBAL_TIMER).stop()
-        if self.flops_profiler is not None and self.flops_profiler.started:
-            fc = self._config.flops_profiler_config
-            self.flops_profiler.stop_profile()
-            self.flops_profiler.print_model_profile(profile_step=self.global_steps, module_depth=fc.module_depth,
-                                                    top_modules=fc.top_modules, detailed=fc.detailed,
-                                                    output_file=fc.output_file)
-            self.flops_profiler.end_profile()
+        if self.flops_profiler is not None and self.flops_profiler.started and self.flops_profiler.func_patched:
+            self.flops_profiler.stop_profile()      # counting ends with the forward; the report waits for bwd / step times
         return loss
 
     def _uses_wrapper_backward(self) -> bool:
@@ -655,6 +651,11 @@ class DeepSpeedEngine(torch.nn.Module):
         self.tput_timer.stop(global_step=self.is_gradient_accumulation_boundary(), report_speed=report)
         self.timers(STEP_MICRO_TIMER).stop()
         self.timers(STEP_GLOBAL_TIMER).stop()
+        if self.flops_profiler is not None and self.flops_profiler.started and report:
+            fc = self._config.flops_profiler_config
+            self.flops_profiler.print_model_profile(profile_step=fc.profile_step, module_depth=fc.module_depth,
+                                                    top_modules=fc.top_modules, detailed=fc.detailed, output_file=fc.output_file)
+            self.flops_profiler.end_profile()
         if report:
             if self.monitor.enabled and self.global_rank == 0:
                 events = [("Train/Samples/lr", self.get_lr()[0], self.global_samples)]

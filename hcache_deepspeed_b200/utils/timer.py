@@ -85,20 +85,22 @@ class SynchronizedWallClockTimer:
             self._closed.append(self._open)
             self._open = None
 
-        def _drain(self) -> List[float]:
-            self._last_ms = [iv.milliseconds() for iv in self._closed]
-            self._closed = []
+        def _spans_ms(self) -> List[float]:
+            """Milliseconds of every closed span (device events are resolved once and cached as plain numbers)."""
+            self._closed = [iv if isinstance(iv, float) else iv.milliseconds() for iv in self._closed]
+            self._last_ms = list(self._closed)
             return self._last_ms
 
         def reset(self):
             self._open, self._closed, self._last_ms = None, [], []
 
         def elapsed(self, reset: bool = True) -> float:
-            """Milliseconds accumulated so far; a running timer is paused for the reading and resumed afterwards."""
+            """Milliseconds accumulated so far; a running timer is paused for the reading and resumed afterwards. With
+            ``reset=False`` the accumulated spans are kept, so a later reading still includes them."""
             was_running = self.running
             if was_running:
                 self.stop()
-            total = sum(self._drain())
+            total = sum(self._spans_ms())
             if reset:
                 self.reset()
             if was_running:
@@ -109,7 +111,7 @@ class SynchronizedWallClockTimer:
             was_running = self.running
             if was_running:
                 self.stop()
-            ms = self._drain()
+            ms = self._spans_ms()
             if was_running:
                 self.start()
             return sum(ms) / len(ms) if ms else 0.0
@@ -119,6 +121,9 @@ class SynchronizedWallClockTimer:
 
     def get_timers(self):
         return self.timers
+
+    def has_timer(self, name: str) -> bool:
+        return name in self.timers
 
     def __call__(self, name: str) -> "SynchronizedWallClockTimer.Timer":
         timer = self.timers.get(name)

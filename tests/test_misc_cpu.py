@@ -871,3 +871,66 @@ def test_comms_logger_enabled_from_training_config():
     finally:
         C.comms_logger.enabled, C.comms_logger.prof_all, C.comms_logger.prof_ops, C.comms_logger.verbose = saved
         C.comms_logger.comms_dict.clear()
+
+
+def test_flops_profiler_counts_and_engine_report(tmp_path):
+    """FLOPs profiler (ref: profiling/flops_profiler/profiler.py): exact MAC counts for linear / einsum / baddbmm / conv /
+    attention, restored functionals afterwards, and the training-engine report (summary with bwd / step latency,
+    per-depth top modules, detailed tree with percentages) written at the end of the profiled step."""
+    import torch.nn.functional as F
+    import hcache_deepspeed_b200 as ds
+    from hcache_deepspeed_b200.profiling.flops_profiler.profiler import FlopsProfiler, get_model_profile
+
+    class Net(torch.nn.Module):
+        def __init__(self):
+            super().__init__()
+            self.a, self.conv = torch.nn.Linear(16, 32), torch.nn.Conv1d(4, 6, 3, padding=1)
+
+        def forward(self, x, y):
+            h = self.a(x)                                                  # 5*16*32 MACs
+            e = torch.einsum("bi,ci->bc", h, h)                            # 5*5*32
+            bb = torch.baddbmm(torch.zeros(2, 3, 3), torch.ones(2, 3, 4), torch.ones(2, 4, 3))     # 2*3*4*3
+            c = self.conv(y)                                               # out elems (2*6*8) * (4*3)
+            q = torch.ones(1, 2, 5, 8)
+            s = F.scaled_dot_product_attention(q, q, q)                    # 2 * 5*5*(8+8)
+            return h.sum() + e.sum() + bb.sum() + c.sum() + s.sum()
+
+    net = Net()
+    orig_linear, orig_einsum = F.linear, torch.einsum
+    flops, macs, params = get_model_profile(net, args=(torch.ones(5, 16), torch.ones(2, 4, 8)), print_profile=False, as_string=False)
+    want = 5 * 16 * 32 + 5 * 5 * 32 + 2 * 3 * 4 * 3 + 2 * 6 * 8 * 4 * 3 + 2 * 5 * 5 * 16
+    assert macs == want and flops >= 2 * want and params == sum(p.numel() for p in net.parameters())
+    assert F.linear is orig_linear and torch.einsum is orig_einsum                      # patches removed
+
+    out_file = tmp_path / "flops.txt"
+    model = torch.nn.Sequential(torch.nn.Linear(8, 16), torch.nn.GELU(), torch.nn.Linear(16, 1))
+    cfg = {"train_micro_batch_size_per_gpu": 4, "gradient_accumulation_steps": 2, "optimizer": {"type": "SGD", "params": {"lr": 0.01}},
+           "wall_clock_breakdown": True, "steps_per_print": 100,
+           "flops_profiler": {"enabled": True, "profile_step": 1, "top_modules": 2, "detailed": True, "output_file": str(out_file)}}
+    engine, _, _, _ = ds.initialize(model=model, config=cfg)
+    for i in range(6):
+        loss = engine(torch.randn(4, 8)).pow(2).mean()
+        engine.backward(loss)
+        engine.step()
+        if i < 3:
+            assert not out_file.exists()          # written at the END of global step 1 (micro-steps 2 and 3), not before
+    text = out_file.read_text()
+    for needle in ("Profile Summary at step 1", "data parallel size", "bwd latency", "step latency", "iter latency", "samples/second",
+                   "Aggregated Profile per GPU", "depth 1:", "Detailed Profile per GPU", "(0): Linear(", "% MACs", "fwd MACs:             576.00 MACs"):
+        assert needle in text, needle
+    assert not engine.flops_profiler.started
+
+
+def test_timer_elapsed_without_reset_keeps_the_total():
+    import time as _t
+    from hcache_deepspeed_b200.utils.timer import SynchronizedWallClockTimer
+    timers = SynchronizedWallClockTimer()
+    t = timers("x")
+    for _ in range(2):
+        t.start()
+        _t.sleep(0.01)
+        t.stop()
+    first = t.elapsed(reset=False)
+    assert first >= 15 and abs(t.elapsed(reset=False) - first) < 1e-6 and abs(t.mean() - first / 2) < 1e-6
+    assert t.elapsed(reset=True) == first and t.elapsed() == 0.0
+    assert timers.has_timer("x") and not timers.has_timer("y")
