@@ -85,7 +85,7 @@ class InferenceEngine(torch.nn.Module):
             if config.tensor_parallel.tp_size > 1:
                 from ..module_inject.auto_tp import AutoTP
                 AutoTP.apply(self.module, self.mp_world_size, torch.distributed.get_rank(self.inference_mp_group),
-                             self.inference_mp_group)
+                             self.inference_mp_group, injection_policy=config.injection_policy)
             self._convert_to_dtype(config)
             self.module.to(self.device)
         if config.save_mp_checkpoint_path:

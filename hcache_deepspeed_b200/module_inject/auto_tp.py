@@ -305,8 +305,12 @@ class AutoTP:
 
     # ---- entry point -----------------------------------------------------------------------------------
     @staticmethod
-    def apply(model: nn.Module, mp_size: int, rank: int, mp_group, replace_lm_head: bool = True) -> nn.Module:
-        """Shard ``model`` in place over ``mp_group`` (``mp_size`` ranks, this process is ``rank``)."""
+    def apply(model: nn.Module, mp_size: int, rank: int, mp_group, replace_lm_head: bool = True,
+              injection_policy: Optional[Dict] = None) -> nn.Module:
+        """Shard ``model`` in place over ``mp_group`` (``mp_size`` ranks, this process is ``rank``).
+        ``injection_policy``: ``{BlockClass: ("attn.out_proj", "mlp.fc2")}`` — the user names the row-parallel linears of
+        each block class instead of the parser guessing them (``init_inference(..., injection_policy=...)``,
+        ref inference/engine.py:147-165)."""
         if mp_size <= 1:
             return model
         cfg = getattr(model, "config", None)
@@ -325,8 +329,18 @@ class AutoTP:
             set_n_embd(cfg.hidden_size)
         n_q = next((getattr(cfg, a) for a in ("num_attention_heads", "n_head", "num_heads", "n_heads")
                     if cfg is not None and isinstance(getattr(cfg, a, None), int)), None)
-        policies = AutoTP.tp_parser(model)
-        by_type: Dict[str, List[str]] = {type(m).__name__: gems for m, gems in policies}
+        if injection_policy:
+            by_type: Dict[str, List[str]] = {}
+            for cls, names in injection_policy.items():
+                names = [names] if isinstance(names, str) else list(names)
+                by_type[cls if isinstance(cls, str) else cls.__name__] = names
+            present = {type(m).__name__ for m in model.modules()}
+            missing = [k for k in by_type if k not in present]
+            if missing:
+                raise ValueError(f"injection_policy names module classes the model does not contain: {missing}")
+        else:
+            policies = AutoTP.tp_parser(model)
+            by_type = {type(m).__name__: gems for m, gems in policies}
         for module in model.modules():
             tname = type(module).__name__
             if tname in by_type and not getattr(module, "_autotp_done", False):

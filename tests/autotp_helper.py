@@ -163,3 +163,46 @@ def v1_inject_tp_worker(rank, world, kinds):
         gen = eng.generate(ids, max_new_tokens=4, do_sample=False)
         out[kind] = {"err": float((got - want).abs().max()), "injected": bool(eng.injected), "gen_equal": bool(torch.equal(gen, want_gen))}
     return out
+
+
+def injection_policy_worker(rank, world):
+    """``init_inference(model, tensor_parallel=..., injection_policy={Block: (row-parallel linears)})`` on a model whose
+    layer names the parser could not guess."""
+    import hcache_deepspeed_b200 as ds
+    from hcache_deepspeed_b200.module_inject import LinearAllreduce, LinearLayer
+    ds.init_distributed(dist_backend="gloo")
+
+    class OddBlock(nn.Module):
+        def __init__(self, h):
+            super().__init__()
+            self.first, self.merge = nn.Linear(h, 2 * h), nn.Linear(2 * h, h)     # "merge" is the row-parallel one
+
+        def forward(self, x):
+            return x + self.merge(torch.relu(self.first(x)))
+
+    class OddLM(nn.Module):
+        def __init__(self):
+            super().__init__()
+            self.layers = nn.ModuleList([OddBlock(16) for _ in range(2)])
+
+        def forward(self, x):
+            for l in self.layers:
+                x = l(x)
+            return x
+
+    torch.manual_seed(0)
+    model = OddLM().eval()
+    x = torch.randn(3, 16)
+    with torch.no_grad():
+        want = model(x)
+    bad = None
+    try:
+        ds.init_inference(OddLM(), dtype=torch.float32, tensor_parallel={"tp_size": world}, injection_policy={"NoSuchBlock": ("merge", )})
+    except ValueError as e:
+        bad = str(e)
+    eng = ds.init_inference(model, dtype=torch.float32, tensor_parallel={"tp_size": world}, injection_policy={OddBlock: ("merge", )})
+    with torch.no_grad():
+        got = eng(x)
+    blk = model.layers[0]
+    return {"err": float((got - want).abs().max()), "types": [type(blk.first).__name__, type(blk.merge).__name__],
+            "bad": bad}

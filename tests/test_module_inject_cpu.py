@@ -94,3 +94,10 @@ def test_v1_kernel_inject_under_tensor_parallelism_hf_models():
     for r in run_distributed(v1_inject_tp_worker, 2, kinds, timeout=600):
         for k in kinds:
             assert r[k]["injected"] and r[k]["err"] < 1e-4 and r[k]["gen_equal"], (k, r[k])
+
+
+def test_init_inference_injection_policy_names_row_parallel_linears():
+    from tests.autotp_helper import injection_policy_worker
+    for r in run_distributed(injection_policy_worker, 2):
+        assert r["types"] == ["LinearLayer", "LinearAllreduce"] and r["err"] < 1e-5, r
+        assert "NoSuchBlock" in r["bad"]
