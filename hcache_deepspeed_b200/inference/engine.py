@@ -170,14 +170,25 @@ class InferenceEngine(torch.nn.Module):
         mt = getattr(getattr(self.module, "config", None), "model_type", None)
         if mt not in MODEL_TYPE_TO_POLICY:
             raise ValueError(f"kernel injection is not available for model type {mt}; supported: {sorted(MODEL_TYPE_TO_POLICY)}")
-        dtype = cfg.dtype if (self.device.type == "cuda" or cfg.dtype == torch.float32) else cfg.dtype
+        dtype = cfg.dtype
+        quant = {}
+        if dtype == torch.int8:
+            # the reference's 8-bit serving (dtype=torch.int8: int8 weights + the int8 GEMMs of its v1 op). Blackwell's
+            # 8-bit tensor-core path is FP8: weights are quantised to E4M3 per output channel, activations per token
+            # (the executor's "wf8af8" mode); everything else runs in bf16 (fp32 on the CPU back end)
+            quant = {"quantization_mode": "wf8af8"}
+            dtype = torch.bfloat16 if self.device.type == "cuda" else torch.float32
+            log_dist("init_inference: dtype=torch.int8 -> 8-bit serving through the E4M3 tensor-core path (wf8af8)", [0])
         if self.device.type == "cuda" and dtype not in (torch.float16, torch.bfloat16):
             raise ValueError("the sm_100a kernels take fp16 or bf16; pass dtype=torch.bfloat16")
+        if cfg.use_triton:
+            log_dist("init_inference: use_triton is ignored (no Triton kernels in this build; the native sm_100a kernels run)", [0])
         state = {"max_tracked_sequences": max(hc.max_sessions, 8), "max_ragged_batch_size": hc.max_batch_tokens,
                  "max_ragged_sequence_count": min(max(hc.max_sessions, 8), hc.max_batch_tokens, 512),
                  "max_context": hc.max_context, "memory_config": {"mode": "allocate", "size": hc.kv_memory_bytes}}
         ecfg = RaggedInferenceEngineConfig(tensor_parallel={"tp_size": cfg.tensor_parallel.tp_size}, state_manager=state,
-                                           hcache={"enabled": True, "capture": "sync" if hc.enabled else "off"})
+                                           hcache={"enabled": True, "capture": "sync" if hc.enabled else "off"},
+                                           **({"quantization": quant} if quant else {}))
         policy = MODEL_TYPE_TO_POLICY[mt](self.module.config, checkpoint_engine=InMemoryModelEngine(self.module), dtype=dtype,
                                           device=self.device)
         self._engine = InferenceEngineV2(policy, ecfg)

@@ -249,3 +249,23 @@ def test_diffusers_transformer_block_matches_equivalent_module():
     with torch.no_grad():
         torch.testing.assert_close(fused(x, context=ctx), blk(x, ctx), atol=1e-5, rtol=1e-5)
         torch.testing.assert_close(fused(x, encoder_hidden_states=ctx), blk(x, ctx), atol=1e-5, rtol=1e-5)
+
+
+def test_int8_dtype_selects_8bit_serving():
+    """``init_inference(dtype=torch.int8, replace_with_kernel_inject=True)``: the reference's 8-bit serving request maps to
+    the executor's 8-bit tensor-core mode (E4M3 weights + per-token activations); logits track the fp32 model."""
+    transformers = pytest.importorskip("transformers")
+    import copy
+    import hcache_deepspeed_b200 as ds
+    from hcache_deepspeed_b200.ops.fp8 import Fp8Weight
+    torch.manual_seed(0)
+    model = transformers.LlamaForCausalLM(transformers.LlamaConfig(
+        hidden_size=128, num_hidden_layers=2, num_attention_heads=4, vocab_size=120, max_position_embeddings=128,
+        intermediate_size=256, num_key_value_heads=2)).eval().float()
+    ids = torch.randint(1, 120, (1, 20))
+    with torch.no_grad():
+        want = model(ids).logits
+    eng = ds.init_inference(copy.deepcopy(model), dtype=torch.int8, replace_with_kernel_inject=True)
+    got = eng(ids).logits
+    assert isinstance(eng.ragged_engine.model().w.layers[0].w_qkv, Fp8Weight)
+    assert torch.nn.functional.cosine_similarity(got.flatten(), want.flatten(), dim=0) > 0.99
