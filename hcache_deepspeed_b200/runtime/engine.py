@@ -827,6 +827,8 @@ class DeepSpeedEngine(torch.nn.Module):
 
     def load_checkpoint(self, load_dir, tag=None, load_module_strict: bool = True, load_optimizer_states: bool = True,
                         load_lr_scheduler_states: bool = True, load_module_only: bool = False, custom_load_fn=None):
+        if self._config.load_universal_checkpoint:
+            return self._load_universal_checkpoint(load_dir, tag, load_optimizer_states, load_lr_scheduler_states, load_module_only)
         if tag is None:
             latest = os.path.join(load_dir, "latest")
             if not os.path.isfile(latest):
@@ -899,6 +901,48 @@ class DeepSpeedEngine(torch.nn.Module):
                     "global_steps", "global_samples", "dp_world_size", "mp_world_size", "ds_config", "ds_version"}
         client_state = {k: v for k, v in ckpt.items() if k not in reserved}
         return os.path.join(load_dir, str(tag)), client_state
+
+    def _load_universal_checkpoint(self, load_dir, tag, load_optimizer_states, load_lr_scheduler_states, load_module_only):
+        """``"checkpoint": {"load_universal": true}``: ``load_dir/tag`` (tag defaults to the content of ``latest_universal``)
+        is a folder written by ``ds_to_universal``; every rank cuts ITS slices out of the per-parameter files, so the run
+        may use another data-parallel degree / ZeRO stage (1, 2 or none) than the one that saved (ref: engine.py
+        load_checkpoint -> _load_zero_checkpoint with load_universal_checkpoint())."""
+        from ..checkpoint.universal_checkpoint import load_universal_into_engine
+        if self.zero_optimization_stage() == 3:
+            raise NotImplementedError("universal checkpoints load into ZeRO stage 0 / 1 / 2 (and BF16) optimizers")
+        if tag is None:
+            latest = os.path.join(load_dir, "latest_universal")
+            if not os.path.isfile(latest):
+                logger.warning(f"Unable to find {latest}; run ds_to_universal first or pass the universal tag")
+                return None, None
+            with open(latest) as f:
+                tag = f.read().strip()
+        folder = os.path.join(load_dir, str(tag))
+        if not os.path.isdir(os.path.join(folder, "zero")):
+            logger.warning(f"{folder} is not a universal checkpoint (no zero/ folder)")
+            return None, None
+        n = load_universal_into_engine(self, folder, load_optimizer_states=load_optimizer_states and not load_module_only)
+        log_dist(f"universal checkpoint {folder}: {n} parameters restored", ranks=[0])
+        client_state = {}
+        import glob
+        files = sorted(glob.glob(os.path.join(folder, "*model_states.pt")))
+        if files:
+            ckpt = self.checkpoint_engine.load(files[0], map_location="cpu")
+            own = dict(self.module.named_buffers())
+            for k in ckpt.get("buffer_names") or []:
+                if k in own and k in (ckpt.get("module") or {}):
+                    own[k].data.copy_(ckpt["module"][k])
+            if not load_module_only:
+                self.global_steps = ckpt.get("global_steps", 0)
+                self.global_samples = ckpt.get("global_samples", self.global_steps * self.train_batch_size())
+                self.skipped_steps = ckpt.get("skipped_steps", 0)
+                if load_lr_scheduler_states and self.lr_scheduler is not None and ckpt.get("lr_scheduler") is not None:
+                    self.lr_scheduler.load_state_dict(ckpt["lr_scheduler"])
+            reserved = {"module", "buffer_names", "buffers", "optimizer", "param_shapes", "frozen_param_shapes",
+                        "frozen_param_fragments", "shared_params", "lr_scheduler", "skipped_steps", "global_steps",
+                        "global_samples", "dp_world_size", "mp_world_size", "ds_config", "ds_version", "universal_checkpoint_info"}
+            client_state = {k: v for k, v in ckpt.items() if k not in reserved}
+        return folder, client_state
 
     def _zero3_consolidated_16bit_state_dict(self, exclude_frozen_parameters: bool = False):
         from .zero.partition_parameters import GatheredParameters

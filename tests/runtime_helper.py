@@ -209,7 +209,15 @@ def ckpt_tools_worker(rank, world, stage, save_dir, mode):
     model = TinyNet(32)
     cfg = {"train_micro_batch_size_per_gpu": 4, "optimizer": {"type": "AdamW", "params": {"lr": 1e-2, "weight_decay": 0.0}},
            "zero_optimization": {"stage": stage, "stage3_param_persistence_threshold": 0}, "steps_per_print": 1000}
+    if mode == "universal_config":
+        cfg["checkpoint"] = {"load_universal": True}
     engine, _, _, _ = ds.initialize(model=model, config=cfg)
+    if mode == "universal_config":
+        # save_dir is the ORIGINAL checkpoint folder: the tag comes from latest_universal, steps come back too
+        path, client = engine.load_checkpoint(save_dir)
+        m = engine.optimizer.single_partition_of_fp32_groups[0]
+        return {"path": path, "steps": engine.global_steps, "state": {k: v.detach().float().clone() for k, v in engine.module.state_dict().items()},
+                "exp_avg_norm": float(engine.optimizer.optimizer.state[m]["exp_avg"].norm())}
     if mode == "save":
         for x, y in make_batches(3, 4 * world, 32):
             lo = rank * 4

@@ -36,6 +36,12 @@ def test_universal_checkpoint_resumes_with_other_dp_degree(tmp_path):
     assert res[0]["restored"] == len(states[0]) and res[0]["exp_avg_norm"] > 0
     for k, v in states[0].items():
         torch.testing.assert_close(res[0]["state"][k], v, rtol=1e-6, atol=1e-7)
+    # the config switch: "checkpoint": {"load_universal": true} + engine.load_checkpoint(dir) under dp 3 / stage 1
+    res = run_distributed(ckpt_tools_worker, 3, 1, d, "universal_config")
+    for r in res:
+        assert r["path"].endswith("t3_universal") and r["steps"] == 3 and r["exp_avg_norm"] > 0
+        for k, v in states[0].items():
+            torch.testing.assert_close(r["state"][k], v, rtol=1e-6, atol=1e-7)
 
 
 def test_reshape_3d_maps_and_zero_checkpoint(tmp_path):
