@@ -129,6 +129,17 @@ class DeepSpeedEngine(torch.nn.Module):
         self.training_dataloader = self.deepspeed_io(training_data) if training_data is not None else None
         self.checkpoint_engine = None
         self._configure_checkpointing()
+        self._amp_autocast = False
+        if self.amp_enabled():
+            if self.fp16_enabled() or self.bfloat16_enabled():
+                raise ValueError("amp cannot be combined with the fp16 / bf16 blocks (ref: config.py _do_error_check)")
+            if self.zero_optimization_stage() > 0:
+                raise ValueError("amp is not compatible with ZeRO: use the bf16 block")
+            params = self._config.amp_params or {}
+            if str(params.get("dtype", "bf16")).lower() in ("fp16", "float16", "half"):
+                raise NotImplementedError('amp with fp16 autocast is not provided: use "fp16": {"enabled": true}')
+            self._amp_autocast = str(params.get("opt_level", "O1")).upper() != "O0"
+            log_dist(f"amp: fp32 parameters, torch.autocast(bfloat16) {'on' if self._amp_autocast else 'off (O0)'}", ranks=[0])
         self.flops_profiler = None
         if self._config.flops_profiler_config.enabled:
             from ..profiling.flops_profiler.profiler import FlopsProfiler
@@ -485,7 +496,13 @@ class DeepSpeedEngine(torch.nn.Module):
         self.timers(FORWARD_GLOBAL_TIMER).start()
         if self.training_dataloader is None and self.module.training:
             self.tput_timer.start()
-        loss = self.module(*inputs, **kwargs)
+        if self.amp_enabled():
+            # "amp": apex's mixed precision in the reference. Here: fp32 master parameters + torch.autocast to bf16 (the
+            # B200 default; no loss scaling needed). opt_level O0 keeps fp32; fp16 autocast is what the "fp16" block is for.
+            with torch.autocast(device_type=self.device.type, dtype=torch.bfloat16, enabled=self._amp_autocast):
+                loss = self.module(*inputs, **kwargs)
+        else:
+            loss = self.module(*inputs, **kwargs)
         self.timers(FORWARD_MICRO_TIMER).stop()
         self.timers(FORWARD_GLOBAL_TIMER).stop()
         if self.flops_profiler is not None and self.flops_profiler.started and self.flops_profiler.func_patched:

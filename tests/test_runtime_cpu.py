@@ -447,3 +447,40 @@ def test_zero_init_around_huggingface_constructor_2ranks():
         assert r["n_zero"] > 10 and r["worst"] == 0.0            # every rank holds rank 0's HF initialisation
         assert 0.015 < r["wte_std"] < 0.025                      # initializer_range 0.02, not nn.Embedding's N(0, 1)
         assert r["pretrained_worst"] == 0.0 and r["pretrained_logits"] < 1e-5
+
+
+def test_amp_block_runs_the_forward_under_bf16_autocast():
+    """``"amp": {"enabled": true}``: fp32 parameters, forward under torch.autocast(bfloat16) (apex-free counterpart of the
+    reference's amp path); training still converges; O0 keeps fp32; fp16 / ZeRO combinations are refused."""
+    import hcache_deepspeed_b200 as ds
+    seen = {}
+
+    class Net(torch.nn.Module):
+        def __init__(self):
+            super().__init__()
+            self.a, self.b = torch.nn.Linear(8, 16), torch.nn.Linear(16, 1)
+
+        def forward(self, x, y):
+            h = self.a(x)
+            seen["dtype"] = h.dtype
+            return (self.b(torch.relu(h)).float() - y).pow(2).mean()
+
+    base = {"train_micro_batch_size_per_gpu": 8, "optimizer": {"type": "Adam", "params": {"lr": 0.05}}, "steps_per_print": 1000}
+    torch.manual_seed(0)
+    x, y = torch.randn(8, 8), torch.randn(8, 1)
+    engine, _, _, _ = ds.initialize(model=Net(), config=dict(base, amp={"enabled": True, "opt_level": "O1"}))
+    losses = []
+    for _ in range(30):
+        loss = engine(x, y)
+        engine.backward(loss)
+        engine.step()
+        losses.append(float(loss.detach()))
+    assert seen["dtype"] == torch.bfloat16 and next(engine.module.parameters()).dtype == torch.float32
+    assert losses[-1] < 0.5 * losses[0]
+    engine, _, _, _ = ds.initialize(model=Net(), config=dict(base, amp={"enabled": True, "opt_level": "O0"}))
+    engine(x, y)
+    assert seen["dtype"] == torch.float32
+    with pytest.raises(Exception):
+        ds.initialize(model=Net(), config=dict(base, amp={"enabled": True}, bf16={"enabled": True}))
+    with pytest.raises(NotImplementedError):
+        ds.initialize(model=Net(), config=dict(base, amp={"enabled": True, "dtype": "fp16"}))
