@@ -549,8 +549,14 @@ class DeepSpeedEngine(torch.nn.Module):
     def buffered_allreduce_fallback(self, grads=None, elements_per_buffer: int = MEMORY_OPT_ALLREDUCE_SIZE):
         by_dtype: Dict[torch.dtype, list] = {}
         expert: Dict[str, list] = {}
+        sparse_ids = self._sparse_gradient_param_ids()
         for p in self.module.parameters():
             if not p.requires_grad:
+                continue
+            if id(p) in sparse_ids:
+                # "sparse_gradients": embedding rows touched by this rank travel as (row indices, row values) and are
+                # all-gathered; the averaged gradient stays sparse when autograd produced a sparse one
+                self._sparse_allreduce_param(p)
                 continue
             if p.grad is None:
                 p.grad = torch.zeros_like(p)  # every rank must contribute the same buckets
@@ -563,6 +569,48 @@ class DeepSpeedEngine(torch.nn.Module):
         for name, tensors in expert.items():  # expert grads average over the expert-data-parallel group only
             g = groups._get_expert_data_parallel_group(name)
             self._allreduce_buckets(tensors, g, dist.get_world_size(group=g), elements_per_buffer)
+
+    def _sparse_gradient_param_ids(self):
+        """Weights of ``nn.Embedding`` / ``nn.EmbeddingBag`` modules when ``"sparse_gradients": true`` (ref: engine.py
+        sparse_tensor_module_names)."""
+        ids = getattr(self, "_sparse_param_ids", None)
+        if ids is None:
+            ids = set()
+            if self._config.sparse_gradients_enabled:
+                for m in self.module.modules():
+                    if isinstance(m, (torch.nn.Embedding, torch.nn.EmbeddingBag)):
+                        ids.add(id(m.weight))
+            self._sparse_param_ids = ids
+        return ids
+
+    @staticmethod
+    def _all_gather_rows(t: torch.Tensor, group, ws: int):
+        """All-gather tensors whose first dimension differs per rank: sizes first, then padded payloads."""
+        n = torch.tensor([t.shape[0]], dtype=torch.long, device=t.device)
+        sizes = [torch.zeros_like(n) for _ in range(ws)]
+        dist.all_gather(sizes, n, group=group)
+        sizes = [int(x) for x in sizes]
+        cap = max(max(sizes), 1)
+        padded = t.new_zeros((cap, ) + tuple(t.shape[1:]))
+        padded[:t.shape[0]] = t
+        parts = [torch.empty_like(padded) for _ in range(ws)]
+        dist.all_gather(parts, padded, group=group)
+        return [p[:k] for p, k in zip(parts, sizes)]
+
+    def _sparse_allreduce_param(self, p):
+        from .sparse_tensor import SparseTensor
+        ws, group = self.dp_world_size, self.data_parallel_group
+        was_sparse = p.grad is not None and p.grad.is_sparse
+        grad = p.grad if p.grad is not None else torch.zeros_like(p)
+        st = SparseTensor(grad.data)
+        pre = self.gradient_predivide_factor() if self._config.prescale_gradients else ws
+        values = st.values / pre
+        st.indices = torch.cat(self._all_gather_rows(st.indices, group, ws))
+        st.values = torch.cat(self._all_gather_rows(values, group, ws))
+        if pre != ws:
+            st.values = st.values * (pre / ws)
+        self.sparse_allreduce_stats = {"rows_sent": int(st.indices.numel()), "dense_rows": int(p.shape[0])}
+        p.grad = st.to_coo_tensor().coalesce() if was_sparse else st.to_dense().to(p.dtype)
 
     def _allreduce_buckets(self, tensors, group, ws, elements_per_buffer):
         if ws == 1:

@@ -341,3 +341,40 @@ def zero_init_hf_worker(rank, world):
         import shutil
         shutil.rmtree(d, ignore_errors=True)
     return out
+
+
+def sparse_gradients_worker(rank, world, sparse_module):
+    """``"sparse_gradients": true``: embedding gradients are exchanged as (rows, values); the result equals the dense
+    all-reduce average."""
+    import hcache_deepspeed_b200 as ds
+    ds.init_distributed(dist_backend="gloo")
+
+    class Net(torch.nn.Module):
+        def __init__(self):
+            super().__init__()
+            self.emb = torch.nn.Embedding(50, 8, sparse=sparse_module)
+            self.out = torch.nn.Linear(8, 1)
+
+        def forward(self, ids, y):
+            return (self.out(self.emb(ids).mean(1)) - y).pow(2).mean()
+
+    def run(sparse_cfg):
+        torch.manual_seed(0)
+        net = Net()
+        cfg = {"train_micro_batch_size_per_gpu": 4, "optimizer": {"type": "SGD", "params": {"lr": 0.1}}, "steps_per_print": 1000,
+               "sparse_gradients": sparse_cfg}
+        engine, _, _, _ = ds.initialize(model=net, config=cfg)
+        g = torch.Generator().manual_seed(10 + rank)
+        for _ in range(3):
+            ids, y = torch.randint(0, 50, (4, 3), generator=g), torch.randn(4, 1, generator=g)
+            loss = engine(ids, y)
+            engine.backward(loss)
+            engine.step()
+        return engine, net.emb.weight.detach().clone()
+
+    eng_s, w_sparse = run(True)
+    stats = dict(eng_s.sparse_allreduce_stats)
+    if sparse_module:
+        return {"stats": stats, "w": w_sparse}
+    _, w_dense = run(False)
+    return {"stats": stats, "w": w_sparse, "w_dense": w_dense}

@@ -484,3 +484,15 @@ def test_amp_block_runs_the_forward_under_bf16_autocast():
         ds.initialize(model=Net(), config=dict(base, amp={"enabled": True}, bf16={"enabled": True}))
     with pytest.raises(NotImplementedError):
         ds.initialize(model=Net(), config=dict(base, amp={"enabled": True, "dtype": "fp16"}))
+
+
+def test_sparse_gradients_allgather_rows_2ranks():
+    from tests.runtime_helper import sparse_gradients_worker
+    res = run_distributed(sparse_gradients_worker, 2, False)       # dense autograd gradient, exchanged row-sparse
+    for r in res:
+        assert 0 < r["stats"]["rows_sent"] <= 24 < r["stats"]["dense_rows"]
+        torch.testing.assert_close(r["w"], r["w_dense"], rtol=1e-5, atol=1e-6)
+    torch.testing.assert_close(res[0]["w"], res[1]["w"], rtol=0, atol=0)
+    res2 = run_distributed(sparse_gradients_worker, 2, True)        # nn.Embedding(sparse=True): the gradient stays sparse
+    torch.testing.assert_close(res2[0]["w"], res2[1]["w"], rtol=0, atol=0)
+    torch.testing.assert_close(res2[0]["w"], res[0]["w"], rtol=1e-5, atol=1e-6)
