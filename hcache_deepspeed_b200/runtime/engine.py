@@ -281,7 +281,22 @@ class DeepSpeedEngine(torch.nn.Module):
             if not any(is_zero_param(p) for p in model.parameters()):
                 model = model.to(self.device)
         self.module = model
+        self._configure_moe()
         self._broadcast_model()
+
+    def _configure_moe(self):
+        """Expert-parallel process groups for every MoE layer of the module (ref: engine.py _configure_distributed_model:
+        ``module.set_deepspeed_parallelism``), and the bookkeeping the MoE checkpoint layout needs."""
+        from ..moe.layer import MoE
+        self.has_moe_layers, self.num_experts = False, []
+        self._moe_layers = []
+        for name, m in self.module.named_modules():
+            if isinstance(m, MoE):
+                self.has_moe_layers = True
+                self.num_experts.append(m.num_experts)
+                self._moe_layers.append((name, m))
+                if dist.is_initialized():
+                    m.set_deepspeed_parallelism(self._config.use_data_before_expert_parallel_)
 
     def _broadcast_model(self):
         if not dist.is_initialized() or self.dp_world_size_safe() == 1:
@@ -291,7 +306,12 @@ class DeepSpeedEngine(torch.nn.Module):
         for t in list(self.module.parameters()) + list(self.module.buffers()):
             if is_zero_param(t) or not torch.is_tensor(t) or t.numel() == 0:
                 continue
-            if getattr(t, "allreduce", True) is False:  # expert parameters are not replicated over the dp group
+            if getattr(t, "allreduce", True) is False:
+                # expert parameters are replicated over their expert-data-parallel group only
+                g = groups._get_expert_data_parallel_group(t.group_name) if hasattr(t, "group_name") and \
+                    t.group_name in groups._get_expert_data_parallel_group_dict() else None
+                if g is not None and dist.get_world_size(group=g) > 1:
+                    dist.broadcast(t.data, dist.get_global_rank(g, 0), group=g)
                 continue
             dist.broadcast(t.data, src, group=self.data_parallel_group)
 
@@ -838,6 +858,15 @@ class DeepSpeedEngine(torch.nn.Module):
             self.checkpoint_engine.makedirs(os.path.join(save_dir, tag), exist_ok=True)
         if dist.is_initialized():
             dist.barrier()
+        if self.has_moe_layers and self.zero_optimization_stage() < 3:
+            self._save_moe_experts(os.path.join(save_dir, tag))
+            zero_wrapped = isinstance(self.optimizer, (DeepSpeedZeroOptimizer, DeepSpeedZeroOptimizer_Stage3))
+            if self.optimizer is not None and not zero_wrapped and self._moe_layers:
+                # plain optimizers hold the state of THIS rank's experts: one file per expert-parallel rank of the largest group
+                big = max(self._moe_expert_prefixes(), key=lambda t: t[5])
+                if big[3]:
+                    self.checkpoint_engine.save({"optimizer": self.optimizer.state_dict()},
+                                                self._expp_optim_ckpt_name(os.path.join(save_dir, tag), big[2]))
         if self.save_non_zero_checkpoint or self.zero_optimization_stage() == 3:
             self._save_checkpoint(save_dir, tag, client_state, exclude_frozen_parameters)
         if self.save_zero_checkpoint:
@@ -866,6 +895,8 @@ class DeepSpeedEngine(torch.nn.Module):
                         frozen_fragments[name] = p.ds_tensor.detach().cpu().clone()
         else:
             module_sd = self.module_state_dict(exclude_frozen_parameters)
+            if self.has_moe_layers:
+                module_sd = self._strip_expert_keys(module_sd)      # experts live in their own files
             buffers = None
         # tied parameters: alias name -> the name under which the tensor is stored
         seen, shared = {}, {}
@@ -885,6 +916,55 @@ class DeepSpeedEngine(torch.nn.Module):
                      ds_config=self._config._param_dict, ds_version=_version())
         state.update(client_state)
         self.checkpoint_engine.save(state, self._get_ckpt_name(save_dir, tag))
+
+    # ---- mixture-of-experts checkpoint layout (ref: engine.py _save_moe_checkpoint / load_moe_state_dict) -----------------------
+    # layer_<L>_expert_<E>_mp_rank_<MM>_model_states.pt : one file per GLOBAL expert, written by the rank of its expert-data-
+    #                                                      parallel group that has rank 0 there
+    # expp_rank_<R>_mp_rank_<MM>_optim_states.pt        : the (non-ZeRO) optimizer state of expert-parallel rank R
+    # mp_rank_<MM>_model_states.pt                       : everything else (expert tensors removed)
+    @staticmethod
+    def _expert_ckpt_name(ckpt_dir, layer_id, expert_id, mp_rank=0):
+        return os.path.join(ckpt_dir, f"layer_{layer_id}_expert_{expert_id}_mp_rank_{mp_rank:02d}_model_states.pt")
+
+    @staticmethod
+    def _expp_optim_ckpt_name(ckpt_dir, expp_rank, mp_rank=0):
+        return os.path.join(ckpt_dir, f"expp_rank_{expp_rank}_mp_rank_{mp_rank:02d}_optim_states.pt")
+
+    def _moe_expert_prefixes(self):
+        """[(layer id, layer name, ep rank, is writer, ModuleList of local experts, ep size)] for this rank."""
+        out = []
+        for layer_id, (name, m) in enumerate(self._moe_layers):
+            gname = m.expert_group_name
+            ep_rank = dist.get_rank(group=groups._get_expert_parallel_group(gname)) if dist.is_initialized() else 0
+            edp_rank = dist.get_rank(group=groups._get_expert_data_parallel_group(gname)) if dist.is_initialized() else 0
+            out.append((layer_id, name, ep_rank, edp_rank == 0, m.deepspeed_moe.experts.deepspeed_experts, m.ep_size))
+        return out
+
+    def _save_moe_experts(self, ckpt_dir):
+        mp_rank = self.mpu.get_model_parallel_rank() if self.mpu is not None else 0
+        for layer_id, _, ep_rank, writer, experts, _ in self._moe_expert_prefixes():
+            if not writer:
+                continue
+            for local_id, expert in enumerate(experts):
+                gid = ep_rank * len(experts) + local_id
+                sd = {k: v.detach().cpu().clone() for k, v in expert.state_dict().items()}
+                self.checkpoint_engine.save(sd, self._expert_ckpt_name(ckpt_dir, layer_id, gid, mp_rank))
+
+    def _load_moe_experts(self, ckpt_dir, strict: bool = True):
+        mp_rank = self.mpu.get_model_parallel_rank() if self.mpu is not None else 0
+        for layer_id, name, ep_rank, _, experts, _ in self._moe_expert_prefixes():
+            for local_id, expert in enumerate(experts):
+                gid = ep_rank * len(experts) + local_id
+                path = self._expert_ckpt_name(ckpt_dir, layer_id, gid, mp_rank)
+                if not os.path.exists(path):
+                    if strict:
+                        raise FileNotFoundError(f"expert checkpoint {path} is missing (layer {name}, global expert {gid})")
+                    continue
+                expert.load_state_dict(self.checkpoint_engine.load(path, map_location="cpu"), strict=strict)
+
+    def _strip_expert_keys(self, module_sd):
+        drop = [f"{name}.deepspeed_moe.experts.deepspeed_experts." for name, _ in self._moe_layers]
+        return {k: v for k, v in module_sd.items() if not any(k.startswith(d) for d in drop)}
 
     def _save_zero_checkpoint(self, save_dir, tag):
         sd = dict(optimizer_state_dict=self.optimizer.state_dict(), ds_config=self._config._param_dict, ds_version=_version())
@@ -910,6 +990,13 @@ class DeepSpeedEngine(torch.nn.Module):
         if self.zero_optimization_stage() != 3:
             if custom_load_fn is not None:
                 custom_load_fn(src=ckpt["module"], dst=self.module)
+            elif self.has_moe_layers:
+                missing, unexpected = self.module.load_state_dict(ckpt["module"], strict=False)
+                expert_keys = set(self.module.state_dict()) - set(self._strip_expert_keys(self.module.state_dict()))
+                bad = [k for k in missing if k not in expert_keys] + list(unexpected)
+                if bad and load_module_strict:
+                    raise RuntimeError(f"checkpoint does not match the module: {bad[:8]}")
+                self._load_moe_experts(os.path.join(load_dir, str(tag)), strict=load_module_strict)
             else:
                 self.module.load_state_dict(ckpt["module"], strict=load_module_strict)
         else:
@@ -947,7 +1034,13 @@ class DeepSpeedEngine(torch.nn.Module):
                 elif load_optimizer_states:
                     logger.warning(f"ZeRO optimizer state {zpath} not found; optimizer state was not restored")
             elif load_optimizer_states and self.optimizer is not None and ckpt.get("optimizer") is not None:
-                self.optimizer.load_state_dict(ckpt["optimizer"])
+                osd = ckpt["optimizer"]
+                if self.has_moe_layers and self._moe_layers:   # this expert-parallel rank's own optimizer state
+                    big = max(self._moe_expert_prefixes(), key=lambda t: t[5])
+                    own_path = self._expp_optim_ckpt_name(os.path.join(load_dir, str(tag)), big[2])
+                    if os.path.exists(own_path):
+                        osd = self.checkpoint_engine.load(own_path, map_location="cpu")["optimizer"]
+                self.optimizer.load_state_dict(osd)
             if zero_wrapped and not load_optimizer_states and hasattr(self.optimizer, "refresh_fp32_params"):
                 self.optimizer.refresh_fp32_params()
             if load_lr_scheduler_states and self.lr_scheduler is not None and ckpt.get("lr_scheduler") is not None:

@@ -378,3 +378,63 @@ def sparse_gradients_worker(rank, world, sparse_module):
         return {"stats": stats, "w": w_sparse}
     _, w_dense = run(False)
     return {"stats": stats, "w": w_sparse, "w_dense": w_dense}
+
+
+def moe_checkpoint_worker(rank, world, ckpt_dir, mode):
+    """Mixture-of-experts checkpoints: one file per GLOBAL expert, so a run saved with expert parallelism 2 can be loaded
+    with expert parallelism 1 (ref: engine.py _save_moe_checkpoint / load_moe_state_dict)."""
+    import hcache_deepspeed_b200 as ds
+    from hcache_deepspeed_b200.moe.layer import MoE
+    from hcache_deepspeed_b200.moe.utils import split_params_into_different_moe_groups_for_optimizer
+    ds.init_distributed(dist_backend="gloo")
+    torch.manual_seed(0)
+
+    class Net(torch.nn.Module):
+        def __init__(self):
+            super().__init__()
+            self.inp = torch.nn.Linear(8, 16)
+            expert = torch.nn.Sequential(torch.nn.Linear(16, 32), torch.nn.ReLU(), torch.nn.Linear(32, 16))
+            self.moe = MoE(hidden_size=16, expert=expert, num_experts=4, ep_size=world, k=1, capacity_factor=4.0, min_capacity=8)
+            self.out = torch.nn.Linear(16, 1)
+
+        def forward(self, x, y=None):
+            h, aux, _ = self.moe(torch.relu(self.inp(x)))
+            pred = self.out(h)
+            return pred if y is None else (pred - y).pow(2).mean() + 0.01 * aux
+
+    net = Net()
+    groups = split_params_into_different_moe_groups_for_optimizer({"params": list(net.parameters()), "name": "all"})
+    engine, _, _, _ = ds.initialize(model=net, optimizer=torch.optim.AdamW(groups, lr=1e-2),
+                                    config={"train_micro_batch_size_per_gpu": 8, "steps_per_print": 1000})
+    assert engine.has_moe_layers and engine.num_experts == [4]
+    probe = torch.randn(8, 8, generator=torch.Generator().manual_seed(99))
+    if mode == "save":
+        g = torch.Generator().manual_seed(3 + rank)
+        x, y = torch.randn(8, 8, generator=g), torch.randn(8, 1, generator=g)
+        losses = []
+        for _ in range(10):
+            loss = engine(x, y)
+            engine.backward(loss)
+            engine.step()
+            losses.append(float(loss.detach()))
+        engine.save_checkpoint(ckpt_dir, tag="moe")
+        engine.eval()
+        with torch.no_grad():
+            pred = engine(probe)
+        experts = {f"{rank * 2 + i}": [p.detach().clone() for p in e.parameters()]
+                   for i, e in enumerate(net.moe.deepspeed_moe.experts.deepspeed_experts)}
+        # same-degree reload restores the optimizer state of THIS rank's experts too
+        for p in engine.module.parameters():
+            p.data.add_(1.0)
+        engine.load_checkpoint(ckpt_dir, tag="moe")
+        with torch.no_grad():
+            again = engine(probe)
+        st = engine.optimizer.state_dict()["state"]
+        return {"losses": losses, "pred": pred, "again": again, "experts": experts, "files": sorted(os.listdir(os.path.join(ckpt_dir, "moe"))),
+                "opt_entries": len(st)}
+    engine.load_checkpoint(ckpt_dir, tag="moe", load_optimizer_states=False)
+    engine.eval()
+    with torch.no_grad():
+        pred = engine(probe)
+    experts = {f"{i}": [p.detach().clone() for p in e.parameters()] for i, e in enumerate(net.moe.deepspeed_moe.experts.deepspeed_experts)}
+    return {"pred": pred, "experts": experts}

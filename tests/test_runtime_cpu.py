@@ -496,3 +496,22 @@ def test_sparse_gradients_allgather_rows_2ranks():
     res2 = run_distributed(sparse_gradients_worker, 2, True)        # nn.Embedding(sparse=True): the gradient stays sparse
     torch.testing.assert_close(res2[0]["w"], res2[1]["w"], rtol=0, atol=0)
     torch.testing.assert_close(res2[0]["w"], res[0]["w"], rtol=1e-5, atol=1e-6)
+
+
+def test_moe_checkpoint_per_global_expert_reloads_under_other_ep_degree(tmp_path):
+    from tests.runtime_helper import moe_checkpoint_worker
+    d = str(tmp_path / "ck")
+    saved = run_distributed(moe_checkpoint_worker, 2, d, "save")
+    files = saved[0]["files"]
+    assert [f for f in files if f.startswith("layer_0_expert_")] == [f"layer_0_expert_{e}_mp_rank_00_model_states.pt" for e in range(4)]
+    assert "expp_rank_0_mp_rank_00_optim_states.pt" in files and "expp_rank_1_mp_rank_00_optim_states.pt" in files
+    for r in saved:
+        assert r["losses"][-1] < r["losses"][0] and r["opt_entries"] > 0
+        torch.testing.assert_close(r["again"], r["pred"], rtol=0, atol=0)        # same-degree reload is exact
+    one = run_distributed(moe_checkpoint_worker, 1, d, "load")[0]               # ep 2 -> ep 1: all four experts on one rank
+    for r in saved:
+        for gid, tensors in r["experts"].items():
+            for a, b in zip(one["experts"][gid], tensors):
+                torch.testing.assert_close(a, b, rtol=0, atol=0)
+    # token capacity is ample, so routing is the same and the predictions agree with the 2-rank run
+    torch.testing.assert_close(one["pred"], saved[0]["pred"], rtol=1e-5, atol=1e-6)
