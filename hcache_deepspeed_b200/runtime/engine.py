@@ -990,6 +990,8 @@ class DeepSpeedEngine(torch.nn.Module):
         if self.zero_optimization_stage() != 3:
             if custom_load_fn is not None:
                 custom_load_fn(src=ckpt["module"], dst=self.module)
+            elif ckpt.get("module") is None and hasattr(self.module, "load_state_dir"):
+                self.module.load_state_dir(os.path.join(load_dir, str(tag)), self.checkpoint_engine, strict=load_module_strict)
             elif self.has_moe_layers:
                 missing, unexpected = self.module.load_state_dict(ckpt["module"], strict=False)
                 expert_keys = set(self.module.state_dict()) - set(self._strip_expert_keys(self.module.state_dict()))

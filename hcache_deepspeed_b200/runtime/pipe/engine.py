@@ -10,6 +10,8 @@ from __future__ import annotations
 
 from typing import Iterable, Optional
 
+import os
+
 import torch
 
 from ... import comm as dist
@@ -307,4 +309,20 @@ class PipelineEngine(DeepSpeedEngine):
         raise PipelineError("Only train_batch() is accessible in pipeline mode.")
 
     def module_state_dict(self, exclude_frozen_parameters=False):
-        return self.module.state_dict()
+        """The pipeline's weights are written one file per layer (``PipelineModule.save_state_dict``), so a checkpoint can
+        be reloaded under another number of stages; the per-rank model-states file carries no module tensors."""
+        ckpt_dir = getattr(self, "_curr_ckpt_path", None)
+        if ckpt_dir is None:
+            return self.module.state_dict()
+        self.module.save_state_dict(ckpt_dir, self.checkpoint_engine, exclude_frozen_params=exclude_frozen_parameters)
+        return None
+
+    def save_checkpoint(self, save_dir, tag=None, client_state=None, save_latest=True, exclude_frozen_parameters=False):
+        if tag is None:
+            tag = f"global_step{self.global_steps}"
+        self._curr_ckpt_path = os.path.join(save_dir, str(tag))
+        try:
+            return super().save_checkpoint(save_dir, tag=tag, client_state=client_state, save_latest=save_latest,
+                                           exclude_frozen_parameters=exclude_frozen_parameters)
+        finally:
+            self._curr_ckpt_path = None

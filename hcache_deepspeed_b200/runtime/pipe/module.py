@@ -8,6 +8,7 @@ Reference: ``deepspeed/runtime/pipe/module.py`` (LayerSpec :31, TiedLayerSpec :7
 _partition_layers :391, tied comms :455-510)."""
 from __future__ import annotations
 
+import os
 import re
 from collections import defaultdict
 from functools import partial
@@ -205,7 +206,10 @@ class PipelineModule(nn.Module):
             funcs = self.forward_funcs[start:end]
             if not isinstance(x, tuple):
                 x = (x, )
-            if self._is_checkpointable(funcs):
+            # a segment whose inputs carry no gradient (token ids into the embedding of the first stage) is run plainly: a
+            # re-entrant checkpoint there would detach its parameters from the graph and they would never get a gradient
+            feeds_grad = any(torch.is_tensor(t) and t.requires_grad for t in x)
+            if self._is_checkpointable(funcs) and (feeds_grad or not torch.is_grad_enabled()):
                 x = self.activation_checkpoint_func(exec_range(start, end), *x)
             else:
                 x = exec_range(start, end)(*x)
@@ -254,8 +258,53 @@ class PipelineModule(nn.Module):
         for key, comm in self.tied_comms.items():
             for attr in comm["weight_attr"]:
                 w = self._tied_weight(comm["module"], attr)
-                if w.grad is not None:
-                    dist.all_reduce(w.grad, group=comm["group"])
+                if not w.requires_grad:
+                    continue
+                if w.grad is None:      # every stage that holds the tied weight must join the collective
+                    w.grad = torch.zeros_like(w)
+                dist.all_reduce(w.grad, group=comm["group"])
+
+    # ---- checkpoints: one file per layer, independent of how the layers are cut into stages -------------------------------
+    # layer_<II>-model_<MM>-model_states.pt (ref: pipe/module.py ckpt_layer_path / save_state_dict / load_state_dir)
+    def _layer_module(self, global_idx: int):
+        """The module that holds layer ``global_idx``'s parameters on this stage (a tied layer resolves to its shared module)."""
+        spec = self._layer_specs[global_idx]
+        if isinstance(spec, TiedLayerSpec):
+            return self.tied_modules[spec.key] if spec.key in self.tied_modules else None
+        f = self.forward_funcs[global_idx - self._local_start]
+        return f if isinstance(f, nn.Module) else None
+
+    def ckpt_layer_path(self, ckpt_dir: str, global_idx: int) -> str:
+        mp = self._grid.get_slice_parallel_rank() if self._grid is not None else 0
+        return os.path.join(ckpt_dir, f"layer_{global_idx:02d}-model_{mp:02d}-model_states.pt")
+
+    def save_state_dict(self, save_dir: str, checkpoint_engine, exclude_frozen_params: bool = False) -> None:
+        dp_rank = self._grid.data_parallel_id if self._grid is not None else 0
+        if dp_rank != 0:
+            return
+        os.makedirs(save_dir, exist_ok=True)
+        for idx in range(self._local_start, self._local_stop):
+            m = self._layer_module(idx)
+            if m is None or not any(True for _ in m.state_dict()):
+                continue
+            sd = {k: v.detach().cpu().clone() for k, v in m.state_dict().items()}
+            if exclude_frozen_params:
+                frozen = {n for n, p in m.named_parameters() if not p.requires_grad}
+                sd = {k: v for k, v in sd.items() if k not in frozen}
+            checkpoint_engine.save(sd, self.ckpt_layer_path(save_dir, idx))
+
+    def load_state_dir(self, load_dir: str, checkpoint_engine, strict: bool = True) -> None:
+        for idx in range(self._local_start, self._local_stop):
+            m = self._layer_module(idx)
+            if m is None or not any(True for _ in m.state_dict()):
+                continue
+            path = self.ckpt_layer_path(load_dir, idx)
+            if not os.path.exists(path):
+                if strict:
+                    raise FileNotFoundError(f"pipeline checkpoint file {path} is missing")
+                continue
+            m.load_state_dict(checkpoint_engine.load(path, map_location="cpu"), strict=strict)
+        self._synchronize_tied_weights()
 
     def get_tied_weights_and_groups(self):
         return [(self._tied_weight(c["module"], a), c["group"]) for c in self.tied_comms.values() for a in c["weight_attr"]]
@@ -284,26 +333,3 @@ class PipelineModule(nn.Module):
         import os
         return os.path.join(checkpoints_path, str(tag), "module")
 
-    def ckpt_layer_path(self, ckpt_dir, local_layer_idx: int):
-        import os
-        idx = local_layer_idx + self._local_start
-        return os.path.join(ckpt_dir, f"layer_{idx:02d}-model_states.pt")
-
-    def save_state_dict(self, save_dir, checkpoint_engine, exclude_frozen_params=False):
-        dp_rank = self._grid.data_parallel_id if self._grid is not None else 0
-        if dp_rank != 0:
-            return
-        import os
-        os.makedirs(save_dir, exist_ok=True)
-        for idx, layer in enumerate(self.forward_funcs):
-            if isinstance(layer, nn.Module) and hasattr(layer, "state_dict"):
-                checkpoint_engine.save(layer.state_dict(), self.ckpt_layer_path(save_dir, idx))
-
-    def load_state_dir(self, load_dir, checkpoint_engine, strict=True):
-        import os
-        for idx, layer in enumerate(self.forward_funcs):
-            if isinstance(layer, nn.Module):
-                path = self.ckpt_layer_path(load_dir, idx)
-                if os.path.exists(path):
-                    layer.load_state_dict(checkpoint_engine.load(path, map_location="cpu"), strict=strict)
-        self._synchronize_tied_weights()

@@ -438,3 +438,60 @@ def moe_checkpoint_worker(rank, world, ckpt_dir, mode):
         pred = engine(probe)
     experts = {f"{i}": [p.detach().clone() for p in e.parameters()] for i, e in enumerate(net.moe.deepspeed_moe.experts.deepspeed_experts)}
     return {"pred": pred, "experts": experts}
+
+
+def pipe_checkpoint_worker(rank, world, ckpt_dir, mode):
+    """Pipeline checkpoints are written one file per LAYER: a run saved with 2 stages reloads with 1 stage (and with 2).
+    Also covers activation checkpointing on the first stage (token ids in: the embedding must still get its gradient) and
+    tied embedding / head weights across stages."""
+    import hcache_deepspeed_b200 as ds
+    from hcache_deepspeed_b200.pipe import LayerSpec, PipelineModule, TiedLayerSpec
+    ds.init_distributed(dist_backend="gloo")
+
+    class Emb(torch.nn.Module):
+        def __init__(self, v, h):
+            super().__init__()
+            self.weight = torch.nn.Parameter(torch.randn(v, h) * 0.1)
+
+        def forward(self, ids):
+            return torch.nn.functional.embedding(ids, self.weight)
+
+    class Block(torch.nn.Module):
+        def __init__(self, h):
+            super().__init__()
+            self.l1, self.l2 = torch.nn.Linear(h, 2 * h), torch.nn.Linear(2 * h, h)
+
+        def forward(self, x):
+            return x + self.l2(torch.relu(self.l1(x)))
+
+    def head(emb, x):
+        return x @ emb.weight.t()
+
+    def loss_fn(logits, labels):
+        return torch.nn.functional.cross_entropy(logits.reshape(-1, logits.shape[-1]), labels.reshape(-1))
+
+    torch.manual_seed(0)
+    layers = [TiedLayerSpec("emb", Emb, 50, 16)] + [LayerSpec(Block, 16) for _ in range(4)] + [TiedLayerSpec("emb", Emb, 50, 16, forward_fn=head)]
+    net = PipelineModule(layers=layers, num_stages=world, loss_fn=loss_fn, partition_method="uniform",
+                         activation_checkpoint_interval=1 if mode == "save" else 0)
+    cfg = {"train_batch_size": 8, "train_micro_batch_size_per_gpu": 2, "optimizer": {"type": "Adam", "params": {"lr": 1e-2}},
+           "steps_per_print": 1000}
+    engine, _, _, _ = ds.initialize(model=net, config=cfg, model_parameters=[p for p in net.parameters() if p.requires_grad])
+    g = torch.Generator().manual_seed(7)
+    data = [(torch.randint(0, 50, (2, 6), generator=g), ) * 2 for _ in range(4)]
+
+    def batches():
+        while True:
+            for d in data:
+                yield d
+
+    if mode == "save":
+        emb0 = net.tied_modules["emb"].weight.detach().clone()
+        losses = [float(engine.train_batch(data_iter=batches())) for _ in range(10)]
+        moved = float((net.tied_modules["emb"].weight.detach() - emb0).abs().max())
+        ev = float(engine.eval_batch(batches()))
+        engine.save_checkpoint(ckpt_dir, tag="p")
+        return {"losses": losses, "eval": ev, "emb_moved": moved, "files": sorted(os.listdir(os.path.join(ckpt_dir, "p"))),
+                "emb_sum": float(net.tied_modules["emb"].weight.detach().sum())}
+    engine.load_checkpoint(ckpt_dir, tag="p", load_optimizer_states=False)
+    return {"eval": float(engine.eval_batch(batches())), "emb_sum": float(net.tied_modules["emb"].weight.detach().sum())}

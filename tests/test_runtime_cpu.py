@@ -515,3 +515,19 @@ def test_moe_checkpoint_per_global_expert_reloads_under_other_ep_degree(tmp_path
                 torch.testing.assert_close(a, b, rtol=0, atol=0)
     # token capacity is ample, so routing is the same and the predictions agree with the 2-rank run
     torch.testing.assert_close(one["pred"], saved[0]["pred"], rtol=1e-5, atol=1e-6)
+
+
+def test_pipeline_layer_checkpoints_reload_under_other_stage_count(tmp_path):
+    from tests.runtime_helper import pipe_checkpoint_worker
+    d = str(tmp_path / "ck")
+    saved = run_distributed(pipe_checkpoint_worker, 2, d, "save")
+    layer_files = [f for f in saved[0]["files"] if f.startswith("layer_")]
+    assert layer_files == [f"layer_{i:02d}-model_00-model_states.pt" for i in range(6)]
+    for r in saved:
+        assert r["losses"][-1] < 0.6 * r["losses"][0]
+        assert r["emb_moved"] > 1e-3                       # the checkpointed first stage still trains its embedding
+    assert saved[0]["emb_sum"] == pytest.approx(saved[1]["emb_sum"], rel=1e-6)      # tied weight identical on both stages
+    one = run_distributed(pipe_checkpoint_worker, 1, d, "load")[0]                  # 2 stages -> 1 stage
+    two = run_distributed(pipe_checkpoint_worker, 2, d, "load")
+    assert one["eval"] == pytest.approx(saved[0]["eval"], rel=1e-5) and two[0]["eval"] == pytest.approx(saved[0]["eval"], rel=1e-5)
+    assert one["emb_sum"] == pytest.approx(saved[0]["emb_sum"], rel=1e-6)
