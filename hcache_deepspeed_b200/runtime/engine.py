@@ -892,7 +892,9 @@ class DeepSpeedEngine(torch.nn.Module):
                 for name, p in self.module.named_parameters():
                     if not p.requires_grad and hasattr(p, "ds_tensor"):
                         frozen_shapes[name] = torch.Size(p.ds_shape)
-                        frozen_fragments[name] = p.ds_tensor.detach().cpu().clone()
+                        from .zero.partition_parameters import read_partition, release_partition
+                        frozen_fragments[name] = read_partition(p).detach().cpu().clone()
+                        release_partition(p)
         else:
             module_sd = self.module_state_dict(exclude_frozen_parameters)
             if self.has_moe_layers:
@@ -1017,7 +1019,8 @@ class DeepSpeedEngine(torch.nn.Module):
                         if load_module_strict:
                             raise KeyError(f"frozen parameter {name} of the checkpoint is not a ZeRO-3 parameter of this module")
                         continue
-                    p.ds_tensor.copy_(frag.to(p.ds_tensor.dtype))
+                    from .zero.partition_parameters import write_partition
+                    write_partition(p, frag)
                     if p.ds_status == ZeroParamStatus.AVAILABLE:
                         p.ds_status = ZeroParamStatus.NOT_AVAILABLE
                         all_gather_params([p])

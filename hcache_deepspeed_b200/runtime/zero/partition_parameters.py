@@ -39,6 +39,50 @@ def is_zero_param(p) -> bool:
     return hasattr(p, "ds_id")
 
 
+# ---- NVMe tier for parameter partitions (ZeRO-Infinity; ref: partition_parameters.py + swap_tensor/partitioned_param_swapper.py) ----
+# With ``offload_param.device = "nvme"`` a partition big enough for direct I/O lives in a file between uses:
+# ``read_partition`` brings it into a pinned staging buffer, ``release_partition`` gives the buffer back (the file stays
+# valid), ``write_partition`` stores new values and writes them out again. Small partitions stay in host memory.
+_param_swapper = None
+
+
+def set_param_swapper(swapper) -> None:
+    global _param_swapper
+    _param_swapper = swapper
+
+
+def get_param_swapper():
+    return _param_swapper
+
+
+def _on_nvme(p) -> bool:
+    return getattr(p, "ds_nvme", False) and _param_swapper is not None
+
+
+def read_partition(p) -> torch.Tensor:
+    """This rank's slice of ``p`` as a tensor that is valid until ``release_partition(p)``."""
+    if _on_nvme(p):
+        from ..swap_tensor.partitioned_param_swapper import PartitionedParamStatus
+        if getattr(p.ds_tensor, "status", None) != PartitionedParamStatus.AVAILABLE:
+            _param_swapper.swap_in([p], async_op=False)
+    return p.ds_tensor
+
+
+def release_partition(p) -> None:
+    if _on_nvme(p):
+        _param_swapper.remove_partition_and_release_buffers([p])
+
+
+def write_partition(p, values: torch.Tensor) -> None:
+    """Replace this rank's slice of ``p`` (``values``: the slice, or a prefix of it) and persist it."""
+    if _on_nvme(p):
+        read_partition(p)
+        p.ds_tensor[:values.numel()].copy_(values.reshape(-1).to(p.ds_tensor.dtype))
+        _param_swapper.swap_out_and_release([p])
+    else:
+        p.ds_tensor[:values.numel()].copy_(values.reshape(-1).to(p.ds_tensor.dtype))
+
+
 def _group_info(group):
     if dist.is_initialized():
         return dist.get_world_size(group=group), dist.get_rank(group=group)
@@ -78,6 +122,11 @@ def _convert(param: torch.nn.Parameter, group, remote_device: Optional[str], pin
     param.ds_tensor.ds_numel = psize
     param.ds_device = flat.device
     param.ds_status = ZeroParamStatus.AVAILABLE
+    param.ds_nvme = False
+    if remote_device == "nvme" and _param_swapper is not None and _param_swapper.swappable_tensor(numel=psize) and \
+            _param_swapper._aligned(psize) <= _param_swapper.elements_per_buffer and part.dtype == _param_swapper.dtype:
+        param.ds_nvme = True
+        _param_swapper.swap_out_and_release([param])       # the slice now lives in its file
 
     def all_gather(param_list: Optional[List] = None, async_op: bool = False, hierarchy: int = 0):
         all_gather_params(param_list if param_list is not None else [param])
@@ -116,7 +165,7 @@ def _partition_param(p, has_been_updated: bool = False):
         flat = p.data.contiguous().view(-1)
         lo, hi = rank * psize, min(p.ds_numel, (rank + 1) * psize)
         if lo < hi:
-            p.ds_tensor[:hi - lo].copy_(flat[lo:hi])
+            write_partition(p, flat[lo:hi])
     if p.ds_persist:
         return
     p.data = torch.empty(0, dtype=p.dtype, device=p.ds_device)
@@ -137,9 +186,10 @@ def all_gather_params(params: Iterable, async_op: bool = False) -> None:
             continue
         ws, _ = _group_info(p.ds_process_group)
         psize = p.ds_partition_numel
-        local = p.ds_tensor.to(p.ds_device, non_blocking=True)
+        local = read_partition(p).to(p.ds_device, non_blocking=True)
         if ws == 1:
             full = local.clone()
+            release_partition(p)
         else:
             full = torch.empty(psize * ws, dtype=local.dtype, device=p.ds_device)
             p.ds_status = ZeroParamStatus.INFLIGHT
@@ -147,6 +197,7 @@ def all_gather_params(params: Iterable, async_op: bool = False) -> None:
             if async_op:
                 p._ds_inflight = (work, full)
                 continue
+            release_partition(p)
         p.data = full.narrow(0, 0, p.ds_numel).view(p.ds_shape)
         p.ds_status = ZeroParamStatus.AVAILABLE
 
@@ -155,6 +206,7 @@ def _wait_inflight(p) -> None:
     work, full = p._ds_inflight
     if work is not None:
         work.wait()
+    release_partition(p)         # the staging buffer was the collective's source until now
     p._ds_inflight = None
     p.data = full.narrow(0, 0, p.ds_numel).view(p.ds_shape)
     p.ds_status = ZeroParamStatus.AVAILABLE

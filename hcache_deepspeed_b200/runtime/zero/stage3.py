@@ -21,7 +21,8 @@ import torch
 from ... import comm as dist
 from ...utils.logging import logger
 from ..fp16.loss_scaler import CreateLossScaler
-from .partition_parameters import (Init, ZeroParamStatus, _partition_param, all_gather_params, is_zero_param)
+from .partition_parameters import (Init, ZeroParamStatus, _partition_param, all_gather_params, is_zero_param, read_partition,
+                                   release_partition, set_param_swapper, write_partition)
 
 
 class DeepSpeedZeRoOffload:
@@ -37,8 +38,21 @@ class DeepSpeedZeRoOffload:
         self.dp_process_group = dp_process_group
         remote = None
         pin = False
-        if offload_param_config is not None and str(getattr(offload_param_config, "device", "none")).split(".")[-1] in ("cpu", "nvme"):
-            remote, pin = "cpu", bool(getattr(offload_param_config, "pin_memory", False))
+        self.param_swapper = None
+        device_name = str(getattr(offload_param_config, "device", "none")).split(".")[-1] if offload_param_config is not None else "none"
+        if device_name in ("cpu", "nvme"):
+            remote, pin = device_name, bool(getattr(offload_param_config, "pin_memory", False))
+        if device_name == "nvme":
+            # ZeRO-Infinity: partitions live in files under nvme_path, staged through a pool of pinned buffers
+            from ..swap_tensor.partitioned_param_swapper import AsyncPartitionedParameterSwapper
+            first = next((p for p in module.parameters() if p.dtype.is_floating_point), None)
+            model_dtype = dtype if dtype is not None else (first.dtype if first is not None else torch.float32)
+            aio = getattr(ds_config, "aio_config", None)
+            self.param_swapper = AsyncPartitionedParameterSwapper(
+                model_dtype=model_dtype, nvme_path=str(offload_param_config.nvme_path),
+                buffer_count=int(getattr(offload_param_config, "buffer_count", 5)),
+                buffer_size=int(getattr(offload_param_config, "buffer_size", 1e8)), aio_config=dict(aio) if aio else None)
+            set_param_swapper(self.param_swapper)
         init = Init(data_parallel_group=dp_process_group, remote_device=remote, pin_memory=pin, dtype=dtype, enabled=True)
         init.persistence_threshold = param_persistence_threshold
         init._convert_module(module)
@@ -276,7 +290,11 @@ class DeepSpeedZeroOptimizer_Stage3:
                 group["params"] = []
                 continue
             dev = torch.device("cpu") if self.offload_optimizer else params[0].ds_device
-            master = torch.cat([p.ds_tensor.detach().float().view(-1).to(dev) for p in params])
+            pieces = []
+            for p in params:        # NVMe-resident slices are staged one at a time
+                pieces.append(read_partition(p).detach().float().view(-1).to(dev).clone())
+                release_partition(p)
+            master = torch.cat(pieces)
             master.requires_grad = True
             self.fp32_partitioned_groups_flat.append(master)
             group["params"] = [master]
@@ -413,7 +431,7 @@ class DeepSpeedZeroOptimizer_Stage3:
             off = 0
             for p in params:
                 n = p.ds_partition_numel
-                p.ds_tensor.copy_(master.detach().narrow(0, off, n).to(p.ds_tensor.dtype))
+                write_partition(p, master.detach().narrow(0, off, n))
                 off += n
                 if p.ds_status == ZeroParamStatus.AVAILABLE:  # persistent parameters: refresh the resident full copy
                     p.ds_status = ZeroParamStatus.NOT_AVAILABLE
@@ -424,7 +442,7 @@ class DeepSpeedZeroOptimizer_Stage3:
         master.grad = None
         for p in self.fp16_groups[gi]:
             n = p.ds_partition_numel
-            p.ds_tensor.copy_(master.detach().narrow(0, off, n).to(p.ds_tensor.dtype))
+            write_partition(p, master.detach().narrow(0, off, n))
             off += n
             if p.ds_status == ZeroParamStatus.AVAILABLE:  # persistent parameters: refresh the resident full copy
                 p.ds_status = ZeroParamStatus.NOT_AVAILABLE
@@ -512,7 +530,7 @@ class DeepSpeedZeroOptimizer_Stage3:
             master, off = self.fp32_partitioned_groups_flat[gi], 0
             for p in params:
                 n = p.ds_partition_numel
-                p.ds_tensor.copy_(master.detach().narrow(0, off, n).to(p.ds_tensor.dtype))
+                write_partition(p, master.detach().narrow(0, off, n))
                 off += n
                 if p.ds_status == ZeroParamStatus.AVAILABLE:
                     p.ds_status = ZeroParamStatus.NOT_AVAILABLE

@@ -495,3 +495,51 @@ def pipe_checkpoint_worker(rank, world, ckpt_dir, mode):
                 "emb_sum": float(net.tied_modules["emb"].weight.detach().sum())}
     engine.load_checkpoint(ckpt_dir, tag="p", load_optimizer_states=False)
     return {"eval": float(engine.eval_batch(batches())), "emb_sum": float(net.tied_modules["emb"].weight.detach().sum())}
+
+
+def zero3_nvme_param_worker(rank, world, device, nvme_dir):
+    """ZeRO-Infinity parameter tier: with ``offload_param.device = "nvme"`` partitions above the direct-I/O threshold live in
+    files and are staged through pinned buffers for every gather / update; results equal host offload exactly."""
+    import hcache_deepspeed_b200 as ds
+    from hcache_deepspeed_b200.runtime.zero.partition_parameters import get_param_swapper, set_param_swapper
+    ds.init_distributed(dist_backend="gloo")
+    set_param_swapper(None)
+    torch.manual_seed(0)
+
+    class Net(torch.nn.Module):
+        def __init__(self):
+            super().__init__()
+            self.emb = torch.nn.Embedding(6000, 128)            # 3 MB fp32: 1.5 MB per rank, above the 1 MB threshold
+            self.mid = torch.nn.Linear(128, 128)                 # small: stays in host memory
+            self.out = torch.nn.Linear(128, 6000, bias=False)
+
+        def forward(self, ids):
+            return torch.nn.functional.cross_entropy(self.out(torch.tanh(self.mid(self.emb(ids)))).reshape(-1, 6000), ids.reshape(-1))
+
+    off = {"device": device, "pin_memory": False}
+    if device == "nvme":
+        off.update(nvme_path=os.path.join(nvme_dir, f"r{rank}"), buffer_count=4, buffer_size=1_000_000)
+    cfg = {"train_micro_batch_size_per_gpu": 4, "optimizer": {"type": "AdamW", "params": {"lr": 1e-2}}, "steps_per_print": 1000,
+           "zero_optimization": {"stage": 3, "stage3_param_persistence_threshold": 0, "offload_param": off},
+           "aio": {"block_size": 65536, "queue_depth": 4}}
+    net = Net()
+    engine, _, _, _ = ds.initialize(model=net, config=cfg)
+    g = torch.Generator().manual_seed(5 + rank)
+    ids = torch.randint(0, 6000, (4, 12), generator=g)
+    losses = []
+    for _ in range(4):
+        loss = engine(ids)
+        engine.backward(loss)
+        engine.step()
+        losses.append(float(loss.detach()))
+    out = {"losses": losses, "nvme_params": [n for n, p in net.named_parameters() if getattr(p, "ds_nvme", False)]}
+    if device == "nvme":
+        sw = get_param_swapper()
+        files = sorted(os.listdir(sw.swap_folder))
+        out.update(files=files, free_buffers=sw.available_swap_in_buffers(), host_slices=[int(p.ds_tensor.numel()) for p in net.parameters()
+                                                                                           if getattr(p, "ds_nvme", False)])
+        engine.save_checkpoint(os.path.join(nvme_dir, "ck"), tag="t")
+        engine.load_checkpoint(os.path.join(nvme_dir, "ck"), tag="t")
+        out["after_reload"] = float(engine(ids).detach())
+        set_param_swapper(None)
+    return out

@@ -531,3 +531,15 @@ def test_pipeline_layer_checkpoints_reload_under_other_stage_count(tmp_path):
     two = run_distributed(pipe_checkpoint_worker, 2, d, "load")
     assert one["eval"] == pytest.approx(saved[0]["eval"], rel=1e-5) and two[0]["eval"] == pytest.approx(saved[0]["eval"], rel=1e-5)
     assert one["emb_sum"] == pytest.approx(saved[0]["emb_sum"], rel=1e-6)
+
+
+def test_zero3_parameter_partitions_on_nvme_2ranks(tmp_path):
+    from tests.runtime_helper import zero3_nvme_param_worker
+    host = run_distributed(zero3_nvme_param_worker, 2, "cpu", str(tmp_path))
+    nvme = run_distributed(zero3_nvme_param_worker, 2, "nvme", str(tmp_path))
+    for h, n in zip(host, nvme):
+        assert n["losses"] == h["losses"] and n["losses"][-1] < n["losses"][0]        # bit-identical to host offload
+        assert h["nvme_params"] == [] and n["nvme_params"] == ["emb.weight", "out.weight"]
+        assert len(n["files"]) == 2 and all(f.endswith("_param.tensor.swp") for f in n["files"])
+        assert n["free_buffers"] == 4 and n["host_slices"] == [1, 1]                  # nothing staged between steps
+        assert n["after_reload"] < n["losses"][0]
