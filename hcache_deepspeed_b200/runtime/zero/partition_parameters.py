@@ -190,6 +190,11 @@ def all_gather_params(params: Iterable, async_op: bool = False) -> None:
         if ws == 1:
             full = local.clone()
             release_partition(p)
+        elif getattr(p, "ds_quantized_gather", False) and local.dtype.is_floating_point and psize >= QWZ_GROUP:
+            # ZeRO++ qwZ: the slice travels as int8 codes + one (scale) per 256 values, a quarter / half of the bytes
+            # (ref: partition_parameters.py all_gather with quantization, csrc/quantization/swizzled_quantize.cu)
+            full = _quantized_all_gather(local, ws, p.ds_process_group)
+            release_partition(p)
         else:
             full = torch.empty(psize * ws, dtype=local.dtype, device=p.ds_device)
             p.ds_status = ZeroParamStatus.INFLIGHT
@@ -200,6 +205,24 @@ def all_gather_params(params: Iterable, async_op: bool = False) -> None:
             release_partition(p)
         p.data = full.narrow(0, 0, p.ds_numel).view(p.ds_shape)
         p.ds_status = ZeroParamStatus.AVAILABLE
+
+
+QWZ_GROUP = 256
+
+
+def _quantized_all_gather(local: torch.Tensor, ws: int, group) -> torch.Tensor:
+    from ...ops.quantizer import dequantize_int, quantize_int
+    flat = local.reshape(-1)
+    pad = (-flat.numel()) % QWZ_GROUP
+    if pad:
+        flat = torch.cat([flat, flat.new_zeros(pad)])
+    codes, params = quantize_int(flat.float(), flat.numel() // QWZ_GROUP, 8, symmetric=True)
+    all_codes = torch.empty((ws, ) + tuple(codes.shape), dtype=codes.dtype, device=codes.device)
+    all_params = torch.empty((ws, ) + tuple(params.shape), dtype=params.dtype, device=params.device)
+    dist.all_gather_into_tensor(all_codes.view(-1), codes.reshape(-1).contiguous(), group=group)
+    dist.all_gather_into_tensor(all_params.view(-1), params.reshape(-1).contiguous(), group=group)
+    rows = [dequantize_int(all_codes[r], all_params[r], 8, local.dtype).reshape(-1)[:local.numel()] for r in range(ws)]
+    return torch.cat(rows)
 
 
 def _wait_inflight(p) -> None:

@@ -56,6 +56,11 @@ class DeepSpeedZeRoOffload:
         init = Init(data_parallel_group=dp_process_group, remote_device=remote, pin_memory=pin, dtype=dtype, enabled=True)
         init.persistence_threshold = param_persistence_threshold
         init._convert_module(module)
+        self.zero_quantized_weights = bool(zero_quantized_weights)
+        if zero_quantized_weights or zero_quantized_nontrainable_weights:
+            for p in module.parameters():
+                if is_zero_param(p) and (zero_quantized_weights or not p.requires_grad):
+                    p.ds_quantized_gather = True
         self.hooks = []
         self.reduce_fn = None  # set by the optimizer: called with a list of params whose .grad is complete
         # trace-driven prefetch (reference: partitioned_param_coordinator.py record_module / fetch_sub_module): the first
@@ -248,6 +253,8 @@ class DeepSpeedZeroOptimizer_Stage3:
                  zeropp_loco_param=None, log_trace_cache_warnings=False, **unused):
         self.module = module
         self.optimizer = init_optimizer
+        self.zero_quantized_gradients = bool(unused.get("zero_quantized_gradients", False))
+        self.qgz_stats = {"calls": 0, "bytes_sent": 0, "bytes_unquantized": 0}
         self.param_names = param_names or {}
         self.dp_process_group = dp_process_group
         self.partition_count = dist.get_world_size(group=dp_process_group) if dist.is_initialized() else 1
@@ -271,7 +278,9 @@ class DeepSpeedZeroOptimizer_Stage3:
                                                       max_live_parameters=max_live_parameters,
                                                       max_reuse_distance=max_reuse_distance,
                                                       param_persistence_threshold=param_persistence_threshold,
-                                                      offload_param_config=offload_param_config, mpu=mpu, dtype=None)
+                                                      offload_param_config=offload_param_config, mpu=mpu, dtype=None,
+                                                      ds_config=ds_config, zero_quantized_weights=zero_quantized_weights,
+                                                      zero_quantized_nontrainable_weights=zero_quantized_nontrainable_weights)
         self.parameter_offload.reduce_fn = self._reduce_ready_grads
         self.dtype = dtype
         self.loss_scaler = CreateLossScaler(dtype=dtype, static_loss_scale=static_loss_scale,
@@ -346,9 +355,13 @@ class DeepSpeedZeroOptimizer_Stage3:
             if ws > 1:
                 if self.gradient_predivide_factor != 1.0:
                     buf.div_(self.gradient_predivide_factor)
-                out = torch.empty(psize, dtype=buf.dtype, device=buf.device)
-                dist.reduce_scatter_tensor(out, buf, group=self.dp_process_group)
-                out.div_(ws / self.gradient_predivide_factor)
+                if self.zero_quantized_gradients and psize >= 256:
+                    out = self._quantized_reduce_scatter(buf, psize, ws).to(buf.dtype)
+                    out.mul_(self.gradient_predivide_factor)
+                else:
+                    out = torch.empty(psize, dtype=buf.dtype, device=buf.device)
+                    dist.reduce_scatter_tensor(out, buf, group=self.dp_process_group)
+                    out.div_(ws / self.gradient_predivide_factor)
             else:
                 out = buf
             out = out.to(self.gradient_accumulation_dtype)
@@ -357,6 +370,24 @@ class DeepSpeedZeroOptimizer_Stage3:
             else:
                 self.grad_partitions[p.ds_id] = out.clone()
             p.grad = None
+
+    def _quantized_reduce_scatter(self, buf: torch.Tensor, psize: int, ws: int, bits: int = 8) -> torch.Tensor:
+        """ZeRO++ qgZ on one flat group: every rank quantises the ``ws`` slices of its gradient (one scale per 256 values),
+        an all-to-all delivers slice r of every rank to rank r, which dequantises and averages them (ref:
+        coalesced_collectives.py all_to_all_quant_reduce; the two-hop intra / inter-node form collapses on one NVSwitch node)."""
+        from ...ops.quantizer import dequantize_int, quantize_int
+        pp = (psize + 255) // 256 * 256
+        send = torch.zeros(ws, pp, dtype=torch.float32, device=buf.device)
+        send[:, :psize] = buf.view(ws, psize).float()
+        codes, params = quantize_int(send.reshape(-1), ws * pp // 256, bits, symmetric=True)
+        rc, rp = torch.empty_like(codes), torch.empty_like(params)
+        dist.all_to_all_single(rc.view(-1), codes.reshape(-1).contiguous(), group=self.dp_process_group)
+        dist.all_to_all_single(rp.view(-1), params.reshape(-1).contiguous(), group=self.dp_process_group)
+        deq = dequantize_int(rc, rp, bits, torch.float32).reshape(ws, pp)
+        self.qgz_stats["calls"] += 1
+        self.qgz_stats["bytes_sent"] += codes.numel() * codes.element_size() + params.numel() * params.element_size()
+        self.qgz_stats["bytes_unquantized"] += buf.numel() * buf.element_size()
+        return deq.mean(dim=0)[:psize]
 
     def backward(self, loss, retain_graph: bool = False):
         if self.custom_loss_scaler:

@@ -543,3 +543,27 @@ def zero3_nvme_param_worker(rank, world, device, nvme_dir):
         out["after_reload"] = float(engine(ids).detach())
         set_param_swapper(None)
     return out
+
+
+def zeropp_worker(rank, world, qw, qg):
+    """ZeRO++ on one node: int8 weight all-gather (qwZ) and quantised gradient reduce via all-to-all (qgZ). Training tracks
+    the unquantised run closely; traffic accounting shows the saving."""
+    import hcache_deepspeed_b200 as ds
+    ds.init_distributed(dist_backend="gloo")
+    torch.manual_seed(0)
+    model = torch.nn.Sequential(torch.nn.Linear(64, 256), torch.nn.Tanh(), torch.nn.Linear(256, 64), torch.nn.Tanh(), torch.nn.Linear(64, 1))
+    cfg = {"train_micro_batch_size_per_gpu": 8, "optimizer": {"type": "AdamW", "params": {"lr": 3e-3}}, "steps_per_print": 1000,
+           "zero_optimization": {"stage": 3, "stage3_param_persistence_threshold": 0, "zero_quantized_weights": qw,
+                                 "zero_quantized_gradients": qg}}
+    engine, _, _, _ = ds.initialize(model=model, config=cfg)
+    g = torch.Generator().manual_seed(5 + rank)
+    x = torch.randn(8, 64, generator=g)
+    y = x[:, :1] * 2.0 - x[:, 1:2]
+    losses = []
+    for _ in range(40):
+        loss = (engine(x) - y).pow(2).mean()
+        engine.backward(loss)
+        engine.step()
+        losses.append(float(loss.detach()))
+    flagged = sum(1 for p in model.parameters() if getattr(p, "ds_quantized_gather", False))
+    return {"losses": losses, "flagged": flagged, "qgz": dict(engine.optimizer.qgz_stats)}

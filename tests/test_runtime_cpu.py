@@ -543,3 +543,15 @@ def test_zero3_parameter_partitions_on_nvme_2ranks(tmp_path):
         assert len(n["files"]) == 2 and all(f.endswith("_param.tensor.swp") for f in n["files"])
         assert n["free_buffers"] == 4 and n["host_slices"] == [1, 1]                  # nothing staged between steps
         assert n["after_reload"] < n["losses"][0]
+
+
+def test_zeropp_quantized_weights_and_gradients_2ranks():
+    from tests.runtime_helper import zeropp_worker
+    base = run_distributed(zeropp_worker, 2, False, False)
+    qpp = run_distributed(zeropp_worker, 2, True, True)
+    for b, q in zip(base, qpp):
+        assert b["flagged"] == 0 and b["qgz"]["calls"] == 0
+        assert q["flagged"] == 6 and q["qgz"]["calls"] > 0
+        assert q["qgz"]["bytes_sent"] < 0.3 * q["qgz"]["bytes_unquantized"]            # int8 + scales vs fp32
+        assert q["losses"][-1] < 0.2 * q["losses"][0]                                   # still trains
+        assert abs(q["losses"][-1] - b["losses"][-1]) < 0.1 * b["losses"][0]            # and tracks the exact run
