@@ -52,6 +52,8 @@ def zero_worker(rank, world, stage, steps, gas, offload, dtype_name, ckpt_dir):
     cfg = {"train_micro_batch_size_per_gpu": micro, "gradient_accumulation_steps": gas,
            "optimizer": {"type": "AdamW", "params": {"lr": 1e-2, "weight_decay": 0.0}},
            "zero_optimization": {"stage": stage, "stage3_param_persistence_threshold": 0}, "steps_per_print": 1000}
+    if os.environ.get("HDS_TEST_MICS"):
+        cfg["zero_optimization"]["mics_shard_size"] = int(os.environ["HDS_TEST_MICS"])
     if os.environ.get("HDS_TEST_Z3_REUSE") is not None:
         cfg["zero_optimization"]["stage3_max_reuse_distance"] = int(os.environ["HDS_TEST_Z3_REUSE"])
     if offload == "nvme":
@@ -107,6 +109,10 @@ def zero_worker(rank, world, stage, steps, gas, offload, dtype_name, ckpt_dir):
         if stage == 3:
             out["prefetch_stats"] = dict(engine.optimizer.parameter_offload.stats)
             out["persistent"] = sum(1 for p in engine.module.parameters() if p.ds_persist)
+    if stage == 3 and os.environ.get("HDS_TEST_MICS"):
+        g = engine.optimizer.mics_comm_groups
+        out["mics"] = (type(engine.optimizer).__name__, g.param_shard_size, g.param_repli_size,
+                       max(p.ds_partition_numel * g.param_shard_size - p.ds_numel for p in engine.module.parameters()))
     if stage == 3:
         out["offload_stats"] = dict(engine.optimizer.parameter_offload.stats)
         from hcache_deepspeed_b200.runtime.zero import GatheredParameters

@@ -555,3 +555,16 @@ def test_zeropp_quantized_weights_and_gradients_2ranks():
         assert q["qgz"]["bytes_sent"] < 0.3 * q["qgz"]["bytes_unquantized"]            # int8 + scales vs fp32
         assert q["losses"][-1] < 0.2 * q["losses"][0]                                   # still trains
         assert abs(q["losses"][-1] - b["losses"][-1]) < 0.1 * b["losses"][0]            # and tracks the exact run
+
+
+def test_mics_shard_groups_4ranks(monkeypatch):
+    """MiCS (ref: runtime/zero/mics.py): ZeRO-3 partitions inside shard groups of 2, gradients all-reduced across the two
+    replica groups; same training result as plain data parallelism."""
+    monkeypatch.setenv("HDS_TEST_MICS", "2")
+    steps, world = 4, 4
+    want, want_state = reference_run(steps=steps, global_bs=4 * world)
+    res = run_distributed(zero_worker, world, 3, steps, 1, False, "fp32", None)
+    for r in res:
+        assert r["mics"][:3] == ("MiCS_Optimizer", 2, 2) and 0 <= r["mics"][3] < 2      # sliced over 2 ranks, not 4
+        for k, v in want_state.items():
+            torch.testing.assert_close(r["state"][k], v, rtol=2e-4, atol=2e-5)
