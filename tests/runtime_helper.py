@@ -573,3 +573,64 @@ def zeropp_worker(rank, world, qw, qg):
         losses.append(float(loss.detach()))
     flagged = sum(1 for p in model.parameters() if getattr(p, "ds_quantized_gather", False))
     return {"losses": losses, "flagged": flagged, "qgz": dict(engine.optimizer.qgz_stats)}
+
+
+def partition_activations_worker(rank, world):
+    """``checkpointing.configure(mpu, partition_activations=True)``: each model-parallel rank keeps 1/mp of every
+    checkpointed input and all-gathers it for the recomputation; gradients equal the plain run (ref:
+    activation_checkpointing/checkpointing.py partition_activations / gather_partitioned_activations)."""
+    import hcache_deepspeed_b200 as ds
+    from hcache_deepspeed_b200.runtime.activation_checkpointing import checkpointing
+    ds.init_distributed(dist_backend="gloo")
+
+    class MPU:
+        def get_model_parallel_group(self):
+            return torch.distributed.group.WORLD
+
+        def get_model_parallel_world_size(self):
+            return world
+
+        def get_model_parallel_rank(self):
+            return rank
+
+        def get_data_parallel_group(self):
+            return None
+
+        def get_data_parallel_world_size(self):
+            return 1
+
+        def get_data_parallel_rank(self):
+            return 0
+
+    torch.manual_seed(0)                      # replicated weights and inputs, as in a tensor-parallel group
+    net = torch.nn.Sequential(torch.nn.Linear(16, 16), torch.nn.Tanh(), torch.nn.Linear(16, 16))
+    x = torch.randn(6, 16, requires_grad=True)
+    y = net(x).pow(2).sum()
+    y.backward()
+    want = [p.grad.clone() for p in net.parameters()] + [x.grad.clone()]
+    out = {}
+    for cpu in (False, True):
+        for p in net.parameters():
+            p.grad = None
+        x.grad = None
+        checkpointing.configure(MPU(), partition_activations=True, checkpoint_in_cpu=cpu)
+        saved = []
+        orig = checkpointing.partition_activation
+
+        def spy(t, _orig=orig):
+            part = _orig(t)
+            saved.append((t.numel(), part.numel()))
+            return part
+
+        checkpointing.partition_activation = spy
+        try:
+            y2 = checkpointing.checkpoint(net, x).pow(2).sum()
+            y2.backward()
+        finally:
+            checkpointing.partition_activation = orig
+        got = [p.grad.clone() for p in net.parameters()] + [x.grad.clone()]
+        out[f"cpu={cpu}"] = {"err": max(float((a - b).abs().max()) for a, b in zip(got, want)), "loss": float((y - y2).abs()),
+                             "saved": saved}
+    checkpointing.configure(None, partition_activations=False, checkpoint_in_cpu=False)
+    checkpointing.reset()
+    return out

@@ -568,3 +568,11 @@ def test_mics_shard_groups_4ranks(monkeypatch):
         assert r["mics"][:3] == ("MiCS_Optimizer", 2, 2) and 0 <= r["mics"][3] < 2      # sliced over 2 ranks, not 4
         for k, v in want_state.items():
             torch.testing.assert_close(r["state"][k], v, rtol=2e-4, atol=2e-5)
+
+
+def test_partition_activations_across_model_parallel_ranks():
+    from tests.runtime_helper import partition_activations_worker
+    for r in run_distributed(partition_activations_worker, 2):
+        for k, v in r.items():
+            assert v["err"] < 1e-6 and v["loss"] < 1e-6, (k, v)
+            assert v["saved"] and all(part * 2 == full for full, part in v["saved"]), (k, v)      # half of each input kept per rank
