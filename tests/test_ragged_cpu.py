@@ -137,3 +137,78 @@ def test_sequence_descriptor_accounting():
     with pytest.raises(ValueError):
         s.extend_kv_cache(torch.tensor([1, 2, 3], dtype=torch.int32))
     assert s.free_kv_cache([9]).tolist() == [9] and s.cur_allocated_blocks == 1
+
+
+def test_continuous_batching_with_chunked_prefill_matches_sequential_oracle():
+    """A serving loop in the style of the reference's MII scheduler: 20 requests, at most 6 sequences / 96 tokens per
+    forward, prompts fed in chunks of <= 40 tokens next to running decodes (``query`` / ``can_schedule`` / ``put`` /
+    ``flush``). Every request's greedy continuation equals the one it gets alone on a fresh engine, and every KV block is
+    back in the pool at the end."""
+    import random
+    from hcache_deepspeed_b200.inference.v2 import RaggedInferenceEngineConfig, build_engine_from_arch
+    from hcache_deepspeed_b200.inference.v2.scheduling_utils import SchedulingResult
+    from hcache_deepspeed_b200.models.arch import named_arch
+    spec = named_arch("tiny-llama-test")
+    def mk(mem, T=96):
+        cfg = RaggedInferenceEngineConfig(state_manager=dict(max_tracked_sequences=12, max_ragged_batch_size=T, max_ragged_sequence_count=6, max_context=256,
+                                          memory_config=dict(mode="allocate", size=mem)), hcache={"enabled": False})
+        return build_engine_from_arch(spec, cfg, seed=3, dtype=torch.float32, device=torch.device("cpu"))
+    eng = mk(6 << 20)
+    total_blocks = int(eng.free_blocks.min())
+    rng = random.Random(0)
+    g = torch.Generator().manual_seed(0)
+    N = 20
+    prompts = {u: torch.randint(0, spec.vocab, (rng.randint(3, 120),), generator=g) for u in range(N)}
+    target_new = {u: rng.randint(1, 12) for u in range(N)}
+    # oracle: one sequence at a time on a fresh engine
+    oracle = {}
+    ref = mk(8 << 20, 256)
+    for u in range(N):
+        toks = []
+        lg, _ = ref.put([u], [prompts[u]])
+        for _ in range(target_new[u]):
+            t = int(lg[0].argmax()); toks.append(t)
+            lg, _ = ref.put([u], [torch.tensor([t])])
+        ref.flush(u); oracle[u] = toks
+    # continuous batching with chunked prefill (split-fuse): token budget 96, <= 6 sequences per step
+    pending = list(range(N)); active = {}   # uid -> dict(pos, out, last)
+    done = {}
+    steps = 0
+    while pending or active:
+        steps += 1
+        uids, toks = [], []
+        budget = 96
+        # decodes first
+        for u, st in list(active.items()):
+            if st["pos"] >= len(prompts[u]) and len(uids) < 6 and budget > 0:
+                uids.append(u); toks.append(torch.tensor([st["last"]])); budget -= 1
+        # prefill chunks
+        for u in list(active) + pending[:]:
+            if len(uids) >= 6 or budget <= 0: break
+            if u in uids: continue
+            st = active.get(u)
+            pos = st["pos"] if st else 0
+            if pos >= len(prompts[u]): continue
+            n = min(budget, len(prompts[u]) - pos, 40)
+            max_tok, max_blk = eng.query(u, n, int(eng.free_blocks.min()))
+            n = min(n, max_tok)
+            if n <= 0: continue
+            if eng.can_schedule(uids + [u], [int(t.numel()) for t in toks] + [n]) != SchedulingResult.Success:
+                continue
+            if st is None:
+                pending.remove(u); active[u] = st = {"pos": 0, "out": [], "last": None}
+            uids.append(u); toks.append(prompts[u][pos:pos + n]); budget -= n
+        if not uids:
+            raise RuntimeError(f"nothing schedulable: free={eng.free_blocks} active={len(active)}")
+        lg, _ = eng.put(uids, toks)
+        for i, (u, t) in enumerate(zip(uids, toks)):
+            st = active[u]
+            if st["pos"] < len(prompts[u]):
+                st["pos"] += int(t.numel())
+                if st["pos"] < len(prompts[u]): continue       # more prompt chunks to go: logits unused
+            nxt = int(lg[i].argmax()); st["out"].append(nxt); st["last"] = nxt
+            if len(st["out"]) == target_new[u]:
+                done[u] = st["out"]; eng.flush(u); del active[u]
+    bad = [u for u in range(N) if done[u] != oracle[u]]
+    assert not bad, bad
+    assert int(eng.free_blocks.min()) == total_blocks and steps < 60
