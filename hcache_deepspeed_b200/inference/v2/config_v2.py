@@ -26,8 +26,9 @@ class DeepSpeedTPConfig(DeepSpeedConfigModel):
 class QuantizationConfig(DeepSpeedConfigModel):
     quantization_mode: Optional[str] = None
     """Weight quantization mode. The reference's only mode ('wf6af16') is Ampere-only
-    (``modules/heuristics.py:93-104``); accepted values here: None, or 'wf8af8' (E4M3 weights per output channel
-    and activations per token on the fp8 tensor cores — ``modules/implementations.py::Fp8TensorCoreLinear``)."""
+    (``modules/heuristics.py:93-104``); accepted values here: None, 'wf8af8' (E4M3 weights per output channel and
+    activations per token on the fp8 tensor cores — ``modules/implementations.py::Fp8TensorCoreLinear``) or 'wf6af16'
+    (E3M2 weights packed 6 bits each, fed to the same tensor-core kernels — ``Fp6TensorCoreLinear``)."""
 
 
 class HCacheConfig(DeepSpeedConfigModel):
@@ -46,8 +47,6 @@ class HCacheConfig(DeepSpeedConfigModel):
     shard_capture: bool = False
     """Tensor parallel: every rank exports only its 1/tp row slice of each sequence's hidden states (they are
     replicated on the device), to be passed back to ``restore_kv(..., sharded=True)``."""
-    host_ring_bytes: int = 2 << 30
-    """Pinned host staging used for asynchronous capture."""
 
 
 class RaggedInferenceEngineConfig(DeepSpeedConfigModel):
