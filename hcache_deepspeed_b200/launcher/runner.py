@@ -47,6 +47,9 @@ def parse_args(args=None):
     p.add_argument("--enable_each_rank_log", default="None", type=str)
     p.add_argument("--bind_cores_to_rank", action="store_true")
     p.add_argument("--elastic_training", action="store_true")
+    p.add_argument("--autotuning", default="", choices=["", "tune", "run"],
+                   help="tune: search ZeRO stage x micro-batch size with short runs of the script and write the best config; "
+                        "run: tune, then launch the script with that config")
     p.add_argument("user_script", type=str)
     p.add_argument("user_args", nargs=argparse.REMAINDER)
     return p.parse_args(args=args)
@@ -160,6 +163,98 @@ def build_multinode_cmd(args, active_resources, world_info_b64: str, env: Dict[s
     raise NotImplementedError(f"Unknown launcher {args.launcher}")
 
 
+def _config_path_of(user_args: List[str]) -> Optional[str]:
+    for flag in ("--deepspeed_config", "--deepspeed"):
+        for i, a in enumerate(user_args):
+            if a == flag and i + 1 < len(user_args) and user_args[i + 1].endswith(".json"):
+                return user_args[i + 1]
+            if a.startswith(flag + "="):
+                return a.split("=", 1)[1]
+    return None
+
+
+def _with_config_path(user_args: List[str], path: str) -> List[str]:
+    out, skip = [], False
+    for a in user_args:
+        if skip:
+            skip = False
+            continue
+        if a in ("--deepspeed_config", ):
+            skip = True
+            continue
+        if a.startswith("--deepspeed_config="):
+            continue
+        out.append(a)
+    return out + ["--deepspeed_config", path]
+
+
+def run_autotuning(args, active_resources) -> Optional[str]:
+    """``--autotuning tune|run`` (ref: launcher/runner.py run_autotuning + autotuning/autotuner.py): a first short run of
+    the script reports the model size, then the experiments (ZeRO stage x micro-batch size, pruned by the memory model)
+    run through THIS launcher on the active resources; the best config is written to ``<results_dir>/ds_config_optimal.json``."""
+    import json
+    from ..autotuning.autotuner import Autotuner
+    cfg_path = _config_path_of(list(args.user_args))
+    if cfg_path is None:
+        raise ValueError("--autotuning needs the script to be given its config with --deepspeed_config <file.json>")
+    with open(cfg_path) as f:
+        user_cfg = json.load(f)
+    n_gpus = sum(len(s) for s in active_resources.values())
+    base_cmd = [sys.executable, os.path.abspath(sys.argv[0])]
+    for flag, val in (("--num_gpus", args.num_gpus), ("--num_nodes", args.num_nodes)):
+        if val and val > 0:
+            base_cmd += [flag, str(val)]
+    if args.hostfile and os.path.isfile(args.hostfile):
+        base_cmd += ["-H", args.hostfile]
+    if args.include:
+        base_cmd += ["--include", args.include]
+    if args.master_addr:
+        base_cmd += ["--master_addr", args.master_addr]
+
+    def launch(cfg_file: str, port_offset: int) -> int:
+        cmd = base_cmd + ["--master_port", str(args.master_port + 1 + port_offset), args.user_script] + \
+            _with_config_path(list(args.user_args), cfg_file)
+        return subprocess.run(cmd, stdout=subprocess.DEVNULL, stderr=subprocess.DEVNULL).returncode
+
+    at_cfg = dict(user_cfg.get("autotuning") or {})
+    results_dir = at_cfg.get("results_dir", "autotuning_results")
+    os.makedirs(results_dir, exist_ok=True)
+    info_path = os.path.join(results_dir, "model_info.json")
+    probe = dict(user_cfg)
+    probe["autotuning"] = dict(at_cfg, enabled=True, model_info_path=info_path, model_info={"profile": True})
+    probe_file = os.path.join(results_dir, "ds_config_model_info.json")
+    with open(probe_file, "w") as f:
+        json.dump(probe, f)
+    launch(probe_file, 0)
+    if not os.path.exists(info_path):
+        raise RuntimeError("autotuning: the model-info run wrote no model_info.json (does the script call initialize() with "
+                           "--deepspeed_config and take at least one optimizer step?)")
+    num_params = json.load(open(info_path))["num_params"]
+    counter = {"n": 0}
+
+    def run_fn(cfg):
+        counter["n"] += 1
+        exp_file = os.path.join(results_dir, f"exp_{counter['n']}.json")
+        metric_file = os.path.join(results_dir, f"exp_{counter['n']}_metrics.json")
+        full = dict(cfg)
+        full["autotuning"] = dict(at_cfg, enabled=True, metric_path=metric_file)
+        with open(exp_file, "w") as f:
+            json.dump(full, f)
+        launch(exp_file, counter["n"])
+        if not os.path.exists(metric_file):
+            return None
+        return json.load(open(metric_file)).get(at_cfg.get("metric", "throughput"))
+
+    tuner = Autotuner(user_cfg, num_params=num_params, num_gpus=n_gpus, run_fn=run_fn, results_dir=results_dir)
+    best = tuner.tune()
+    tuner.print_tuning_results()
+    if best is None:
+        return None
+    path = tuner.write_optimal_config()
+    print(f"autotuning: best config written to {path}")
+    return path
+
+
 def main(args=None):
     args = parse_args(args)
     resource_pool = fetch_hostfile(args.hostfile)
@@ -179,6 +274,11 @@ def main(args=None):
         args.master_addr = "127.0.0.1" if not multi_node else \
             subprocess.check_output(["ssh", first, "hostname -I"]).decode().split()[0]
     world_info = encode_world_info(active)
+    if args.autotuning:
+        best = run_autotuning(args, active)
+        if args.autotuning == "tune" or best is None:
+            return
+        args.user_args = _with_config_path(list(args.user_args), best)
     env = os.environ.copy()
     # a source checkout that is not installed: the per-node launcher and the ranks import the package through PYTHONPATH
     # (exported to remote nodes too, "PYTHON" is in EXPORT_ENVS)

@@ -684,6 +684,42 @@ class DeepSpeedEngine(torch.nn.Module):
         self.global_steps += 1
         self.global_samples += self.train_batch_size()
         self._maybe_launch_compile_passes()
+        self._autotuning_hook()
+
+    def _autotuning_hook(self):
+        """Experiment runs of the autotuner (``"autotuning": {"enabled": true, "metric_path": ...}``, written by
+        ``autotuning/autotuner.py``): time the optimizer steps between ``start_profile_step`` and ``end_profile_step``, write
+        the metrics file and leave — the tuner only needs the measurement (ref: engine.py autotuning_profile / exit())."""
+        at = self._config.autotuning_config or {}
+        if not at.get("enabled"):
+            return
+        import json
+        import time
+        info_path = at.get("model_info_path")
+        if info_path and self.global_steps == 1 and self.global_rank == 0:
+            n = sum(getattr(p, "ds_numel", p.numel()) for p in self.module.parameters())
+            os.makedirs(os.path.dirname(info_path) or ".", exist_ok=True)
+            with open(info_path, "w") as f:
+                json.dump({"num_params": int(n), "trainable_params": int(sum(getattr(p, "ds_numel", p.numel())
+                                                                            for p in self.module.parameters() if p.requires_grad))}, f)
+            if at.get("model_info", {}) and at["model_info"].get("profile"):
+                raise SystemExit(0)
+        start, end = int(at.get("start_profile_step", 3)), int(at.get("end_profile_step", 5))
+        if self.device.type == "cuda":
+            torch.cuda.synchronize()
+        if self.global_steps == start:
+            self._autotune_t0 = time.perf_counter()
+        elif self.global_steps >= end and getattr(self, "_autotune_t0", None) is not None:
+            dt = (time.perf_counter() - self._autotune_t0) / max(1, end - start)
+            if self.global_rank == 0 and at.get("metric_path"):
+                os.makedirs(os.path.dirname(at["metric_path"]) or ".", exist_ok=True)
+                with open(at["metric_path"], "w") as f:
+                    json.dump({"latency": dt * 1e3, "throughput": self.train_batch_size() / dt,
+                               "train_micro_batch_size_per_gpu": self.train_micro_batch_size_per_gpu(),
+                               "zero_stage": self.zero_optimization_stage()}, f)
+            if dist.is_initialized():
+                dist.barrier()
+            raise SystemExit(0)
 
     # ---- schedule compiler (the reference's engine.compile / DeepCompile, engine.py:3890+) ---------------------------
     def is_deepcompile_enabled(self) -> bool:

@@ -934,3 +934,51 @@ def test_timer_elapsed_without_reset_keeps_the_total():
     assert first >= 15 and abs(t.elapsed(reset=False) - first) < 1e-6 and abs(t.mean() - first / 2) < 1e-6
     assert t.elapsed(reset=True) == first and t.elapsed() == 0.0
     assert timers.has_timer("x") and not timers.has_timer("y")
+
+
+def test_launcher_autotuning_tune_end_to_end(tmp_path):
+    """``hds --autotuning tune script.py --deepspeed_config cfg.json``: a model-info run, then one short run of the script
+    per (ZeRO stage, micro-batch size) candidate through the launcher; each run's engine writes its metrics file and
+    exits; the best config lands in ``ds_config_optimal.json`` (ref: launcher/runner.py run_autotuning, autotuner.py)."""
+    import json
+    import sys
+    repo = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    script = tmp_path / "train.py"
+    script.write_text(
+        "import argparse, torch\n"
+        "import hcache_deepspeed_b200 as ds\n"
+        "p = argparse.ArgumentParser(); p.add_argument('--local_rank', type=int, default=-1); p.add_argument('--deepspeed_config')\n"
+        "a = p.parse_args()\n"
+        "ds.init_distributed(dist_backend='gloo')\n"
+        "torch.manual_seed(0)\n"
+        "model = torch.nn.Sequential(torch.nn.Linear(32, 64), torch.nn.ReLU(), torch.nn.Linear(64, 1))\n"
+        "engine, _, _, _ = ds.initialize(model=model, config=a.deepspeed_config)\n"
+        "mbs = engine.train_micro_batch_size_per_gpu()\n"
+        "for _ in range(50):\n"
+        "    loss = engine(torch.randn(mbs, 32)).pow(2).mean(); engine.backward(loss); engine.step()\n"
+        "print('TRAINING-FINISHED')\n")
+    results = tmp_path / "results"
+    cfg = {"train_micro_batch_size_per_gpu": 2, "optimizer": {"type": "Adam", "params": {"lr": 1e-3}}, "steps_per_print": 1000,
+           "autotuning": {"enabled": True, "results_dir": str(results), "exps_dir": str(tmp_path / "exps"), "fast": True,
+                          "start_profile_step": 2, "end_profile_step": 4, "micro_batch_sizes": [2, 8], "tuner_num_trials": 4,
+                          "tuner_early_stopping": 10},
+           "zero_optimization": {"stage": 1}}
+    cfg_file = tmp_path / "ds.json"
+    cfg_file.write_text(json.dumps(cfg))
+    env = {k: v for k, v in os.environ.items() if k not in ("PYTHONPATH", "RANK", "WORLD_SIZE", "LOCAL_RANK", "MASTER_ADDR", "MASTER_PORT")}
+    env["CUDA_VISIBLE_DEVICES"] = ""
+    from tests.dist_utils import _free_port
+    out = subprocess.run([sys.executable, os.path.join(repo, "bin", "hds"), "--num_gpus", "1", "--master_port", str(_free_port()),
+                          "--autotuning", "tune", str(script), "--deepspeed_config", str(cfg_file)], cwd=str(tmp_path), env=env,
+                         stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True, timeout=900)
+    assert out.returncode == 0, out.stdout[-3000:]
+    assert "TRAINING-FINISHED" not in out.stdout                      # "tune" does not run the job itself
+    info = json.loads((results / "model_info.json").read_text())
+    assert info["num_params"] == 32 * 64 + 64 + 64 + 1
+    metrics = sorted(results.glob("exp_*_metrics.json"))
+    assert len(metrics) == 2                                           # stage 1 x micro-batch sizes {2, 8}
+    vals = {json.loads(m.read_text())["train_micro_batch_size_per_gpu"]: json.loads(m.read_text())["throughput"] for m in metrics}
+    assert set(vals) == {2, 8} and all(v > 0 for v in vals.values())
+    best = json.loads((results / "ds_config_optimal.json").read_text())
+    assert best["train_micro_batch_size_per_gpu"] == max(vals, key=vals.get) and best["zero_optimization"]["stage"] == 1
+    assert "autotuning: best config written to" in out.stdout
