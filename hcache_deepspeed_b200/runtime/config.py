@@ -250,9 +250,39 @@ class DeepSpeedConfig:
             if mpu is None:
                 world_size = max(1, world_size // max(1, sp) // max(1, tp if tp > 0 else 1))
         self.world_size = world_size
+        self._apply_elasticity()
         self._initialize_params(self._param_dict)
         self._configure_train_batch_size()
         self._do_sanity_check()
+
+    def _apply_elasticity(self):
+        """``"elasticity": {"enabled": true, ...}``: the batch-size triple is DERIVED from the elastic plan for the current
+        world size (global batch = the plan's, micro batch = the largest admissible one, accumulation = what is left);
+        batch sizes given by the user are an error unless ``ignore_non_elastic_batch_info`` (ref: runtime/config.py:739-790)."""
+        pd = self._param_dict
+        el = pd.get("elasticity") or {}
+        if not el.get("enabled", False):
+            return
+        from ..elasticity import compute_elastic_config
+        from ..elasticity.constants import IGNORE_NON_ELASTIC_BATCH_INFO
+        ws = max(1, int(self.world_size or 1))
+        final_bs, valid_gpus, micro = compute_elastic_config(ds_config=pd, world_size=ws, return_microbatch=True)
+        if not el.get(IGNORE_NON_ELASTIC_BATCH_INFO, False):
+            given = [k for k in ("train_batch_size", "train_micro_batch_size_per_gpu", "gradient_accumulation_steps") if k in pd]
+            if given:
+                raise DeepSpeedConfigError(f"elasticity is enabled: {given} must not be set in the config (they follow from the "
+                                           f"elastic plan); remove them or set elasticity.{IGNORE_NON_ELASTIC_BATCH_INFO}")
+        if micro is None:
+            mbs = sorted(el.get("micro_batch_sizes", [1]), reverse=True)
+            micro = next((m for m in mbs if final_bs % (m * ws) == 0), None)
+            if micro is None:
+                raise DeepSpeedConfigError(f"no elastic micro batch size of {mbs} divides batch {final_bs} over {ws} ranks")
+        gas = final_bs // (micro * ws)
+        if gas < 1 or gas * micro * ws != final_bs:
+            raise DeepSpeedConfigError(f"elastic batch {final_bs} cannot be split into micro batches of {micro} over {ws} ranks")
+        pd["train_batch_size"], pd["train_micro_batch_size_per_gpu"], pd["gradient_accumulation_steps"] = final_bs, micro, gas
+        self.elastic_plan = {"train_batch_size": final_bs, "valid_gpus": valid_gpus, "micro_batch_size": micro,
+                             "gradient_accumulation_steps": gas}
 
     # -----------------------------------------------------------------------------------------------
     def _initialize_params(self, pd: dict):

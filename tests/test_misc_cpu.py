@@ -982,3 +982,22 @@ def test_launcher_autotuning_tune_end_to_end(tmp_path):
     best = json.loads((results / "ds_config_optimal.json").read_text())
     assert best["train_micro_batch_size_per_gpu"] == max(vals, key=vals.get) and best["zero_optimization"]["stage"] == 1
     assert "autotuning: best config written to" in out.stdout
+
+
+def test_elasticity_block_drives_the_batch_size_triple():
+    """``"elasticity": {"enabled": true}`` in the training config: global batch from the elastic plan, micro batch and
+    accumulation steps follow from the world size; explicit batch sizes are refused (ref: runtime/config.py:739-790)."""
+    from hcache_deepspeed_b200.runtime.config import DeepSpeedConfig, DeepSpeedConfigError
+    el = {"enabled": True, "max_train_batch_size": 2000, "micro_batch_sizes": [2, 4, 6], "min_gpus": 1, "max_gpus": 10000,
+          "min_time": 20, "version": 0.1}
+    seen = {}
+    for ws in (1, 4, 7, 8):
+        c = DeepSpeedConfig({"elasticity": el}, world_size=ws)
+        assert c.train_batch_size == 1680 == c.train_micro_batch_size_per_gpu * c.gradient_accumulation_steps * ws
+        assert ws in c.elastic_plan["valid_gpus"]
+        seen[ws] = (c.train_micro_batch_size_per_gpu, c.gradient_accumulation_steps)
+    assert seen[4] == (6, 70) and seen[8] == (6, 35)
+    with pytest.raises(DeepSpeedConfigError, match="must not be set"):
+        DeepSpeedConfig({"elasticity": el, "train_batch_size": 8}, world_size=2)
+    c = DeepSpeedConfig({"elasticity": dict(el, ignore_non_elastic_batch_info=True), "train_batch_size": 8}, world_size=2)
+    assert c.train_batch_size == 1680
