@@ -129,6 +129,14 @@ class DeepSpeedEngine(torch.nn.Module):
         self.training_dataloader = self.deepspeed_io(training_data) if training_data is not None else None
         self.checkpoint_engine = None
         self._configure_checkpointing()
+        # compression training: techniques switch on at their schedule offsets as optimizer steps go by (the model must have
+        # been prepared with compression.init_compression; ref: engine.py _configure_compression_scheduler)
+        self.compression_scheduler = None
+        if self._config.compression_config:
+            from ..compression.compress import get_compression_config
+            from ..compression.scheduler import compression_scheduler
+            self.compression_scheduler = compression_scheduler(self.module, get_compression_config(self._config._param_dict))
+            self.compression_scheduler.step(step_zero_check=True)
         self._amp_autocast = False
         if self.amp_enabled():
             if self.fp16_enabled() or self.bfloat16_enabled():
@@ -683,6 +691,8 @@ class DeepSpeedEngine(torch.nn.Module):
                 self.lr_scheduler.step()
         self.global_steps += 1
         self.global_samples += self.train_batch_size()
+        if self.compression_scheduler is not None:
+            self.compression_scheduler.step()
         self._maybe_launch_compile_passes()
         self._autotuning_hook()
 

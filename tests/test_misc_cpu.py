@@ -57,6 +57,33 @@ def test_compression_schedule_and_clean():
     assert len(m.fc2.weight.unique()) <= 17 and float((m.fc2.weight == 0).float().mean()) >= 0.5
 
 
+def test_engine_steps_the_compression_scheduler():
+    """``compression_training`` in the engine config: techniques switch on at their schedule offsets as the engine takes
+    optimizer steps (ref: engine.py _configure_compression_scheduler / _take_model_step)."""
+    import hcache_deepspeed_b200 as ds
+    from hcache_deepspeed_b200.compression import init_compression
+    comp = {"weight_quantization": {"shared_parameters": {"enabled": True, "schedule_offset": 3, "quantize_groups": 1,
+                                                          "quantization_type": "symmetric"},
+                                    "different_groups": {"g": {"params": {"start_bits": 8, "target_bits": 8, "quantization_period": 10},
+                                                               "modules": ["fc1"]}}},
+            "sparse_pruning": {"shared_parameters": {"enabled": True, "schedule_offset": 1, "method": "l1"},
+                               "different_groups": {"s": {"params": {"dense_ratio": 0.5}, "modules": ["fc2"]}}}}
+    cfg = {"train_micro_batch_size_per_gpu": 4, "optimizer": {"type": "SGD", "params": {"lr": 0.01}}, "steps_per_print": 1000,
+           "compression_training": comp}
+    torch.manual_seed(0)
+    m = _MLP()
+    init_compression(m, cfg)
+    engine, _, _, _ = ds.initialize(model=m, config=cfg)
+    assert engine.compression_scheduler is not None
+    seen = []
+    for _ in range(4):
+        loss = engine(torch.randn(4, 16)).pow(2).mean()
+        engine.backward(loss)
+        engine.step()
+        seen.append((m.fc2.sparse_pruning_enabled, m.fc1.weight_quantization_enabled))
+    assert seen == [(True, False), (True, False), (True, True), (True, True)]
+
+
 def test_autotuner_picks_best_feasible_config(tmp_path):
     from hcache_deepspeed_b200.autotuning import Autotuner
 
