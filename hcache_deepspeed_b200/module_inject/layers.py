@@ -89,6 +89,9 @@ class LmHeadLinearAllreduce(torch.nn.Module):
     def forward(self, x: torch.Tensor) -> torch.Tensor:
         sizes = get_shard_size_list(x.shape[-1], self.world_size, "lm_head")
         start = sum(sizes[:self.rank])
+        if self.training and x.requires_grad:
+            # each rank back-propagates into ITS slice of x only: the input gradient is complete after a sum over the group
+            x = ColumnParallel.apply(self.mp_group, x)
         out = torch.matmul(x[..., start:start + sizes[self.rank]], self.weight.transpose(-1, -2))
         out = RowParallel.apply(self.mp_group, out, not self.training)
         return out if self.bias is None else out + self.bias

@@ -206,3 +206,42 @@ def injection_policy_worker(rank, world):
     blk = model.layers[0]
     return {"err": float((got - want).abs().max()), "types": [type(blk.first).__name__, type(blk.merge).__name__],
             "bad": bad}
+
+
+def tp_training_worker(rank, world, tp):
+    """Training-time tensor parallelism (``tp_model_init`` + ``"tensor_parallel": {"autotp_size": tp}``) on a HuggingFace
+    Llama: losses equal the unsharded model's, step by step; with world > tp the remaining ranks are data parallel."""
+    import transformers as T
+    import hcache_deepspeed_b200 as ds
+    from hcache_deepspeed_b200.runtime.tensor_parallel.tp_manager import TpTrainingManager
+    ds.init_distributed(dist_backend="gloo")
+    dp = world // tp
+    torch.manual_seed(0)
+    cfg_m = T.LlamaConfig(hidden_size=64, num_hidden_layers=2, num_attention_heads=4, vocab_size=120, max_position_embeddings=128,
+                          intermediate_size=128, num_key_value_heads=2)
+    model = T.LlamaForCausalLM(cfg_m)
+    g = torch.Generator().manual_seed(5)
+    batches = [torch.randint(1, 120, (2, 16), generator=g) for _ in range(dp)]       # one micro-batch per data-parallel replica
+    ref = T.LlamaForCausalLM(cfg_m)
+    ref.load_state_dict(model.state_dict())
+    opt = torch.optim.SGD(ref.parameters(), lr=0.1)
+    want = []
+    for _ in range(4):
+        losses = [ref(input_ids=b, labels=b).loss for b in batches]
+        (sum(losses) / dp).backward()
+        opt.step()
+        opt.zero_grad()
+        want.append([float(l.detach()) for l in losses])
+    model = ds.tp_model_init(model, tp_size=tp, dtype=torch.float32)
+    engine, _, _, _ = ds.initialize(model=model, config={
+        "train_micro_batch_size_per_gpu": 2, "optimizer": {"type": "SGD", "params": {"lr": 0.1}}, "steps_per_print": 1000,
+        "tensor_parallel": {"autotp_size": tp}, "zero_optimization": {"stage": 1}})
+    mine = TpTrainingManager.broadcast_batch(batches[rank // tp].clone())           # the TP group's ranks share one batch
+    got = []
+    for _ in range(4):
+        loss = engine(input_ids=mine, labels=mine).loss
+        engine.backward(loss)
+        engine.step()
+        got.append(float(loss.detach()))
+    return {"want": [w[rank // tp] for w in want], "got": got, "dp": engine.dp_world_size,
+            "q_rows": model.model.layers[0].self_attn.q_proj.weight.shape[0]}

@@ -101,3 +101,12 @@ def test_init_inference_injection_policy_names_row_parallel_linears():
     for r in run_distributed(injection_policy_worker, 2):
         assert r["types"] == ["LinearLayer", "LinearAllreduce"] and r["err"] < 1e-5, r
         assert "NoSuchBlock" in r["bad"]
+
+
+@pytest.mark.parametrize("world,tp", [(2, 2), (4, 2)])
+def test_training_tensor_parallelism_matches_unsharded_model(world, tp):
+    pytest.importorskip("transformers")
+    from tests.autotp_helper import tp_training_worker
+    for r in run_distributed(tp_training_worker, world, tp, timeout=600):
+        assert r["dp"] == world // tp and r["q_rows"] == 64 // tp
+        assert r["got"] == pytest.approx(r["want"], rel=2e-4, abs=2e-4), r
