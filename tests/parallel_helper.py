@@ -267,3 +267,52 @@ def ccl_backend_worker(rank, world):
     assert shm.attached() is None and not shm.route_all_collectives
     out["name"] = names[0]
     return out
+
+
+def ulysses_engine_worker(rank, world):
+    """Ulysses sequence parallelism THROUGH the training engine (``"sequence_parallel_size": world``): every rank feeds its
+    slice of the sequence, ``DistributedAttention`` all-to-alls heads <-> sequence, gradients are reduced over the
+    sequence-data-parallel group; losses equal full-sequence training on one process."""
+    import torch, traceback, math
+    import hcache_deepspeed_b200 as ds
+    from hcache_deepspeed_b200.sequence.layer import DistributedAttention
+    from hcache_deepspeed_b200.utils import groups
+    ds.init_distributed(dist_backend="gloo")
+    H, NH, S, V = 32, 4, 16, 50
+    def core(q, k, v):   # [b, s, h, d]
+        q, k, v = (t.transpose(1, 2) for t in (q, k, v))
+        return torch.nn.functional.scaled_dot_product_attention(q, k, v, is_causal=True).transpose(1, 2)
+    class Net(torch.nn.Module):
+        def __init__(self, sp_group=None):
+            super().__init__()
+            self.emb = torch.nn.Embedding(V, H); self.qkv = torch.nn.Linear(H, 3 * H); self.o = torch.nn.Linear(H, V)
+            self.attn = DistributedAttention(core, sp_group, scatter_idx=2, gather_idx=1) if sp_group is not None else core
+        def forward(self, ids, labels):
+            x = self.emb(ids); b, s, _ = x.shape
+            q, k, v = self.qkv(x).view(b, s, 3, NH, H // NH).unbind(2)
+            logits = self.o(self.attn(q, k, v).reshape(b, s, H))
+            return torch.nn.functional.cross_entropy(logits.reshape(-1, V), labels.reshape(-1), reduction="sum")
+    if True:
+        torch.manual_seed(0)
+        ref = Net()
+        g = torch.Generator().manual_seed(3)
+        ids = torch.randint(0, V, (2, S), generator=g); labels = torch.randint(0, V, (2, S), generator=g)
+        import copy
+        sd = copy.deepcopy(ref.state_dict())
+        opt = torch.optim.SGD(ref.parameters(), lr=0.05)
+        want = []
+        for _ in range(4):
+            l = ref(ids, labels) / (2 * S); l.backward(); opt.step(); opt.zero_grad(); want.append(round(float(l.detach()), 5))
+        cfg = {"train_micro_batch_size_per_gpu": 2, "optimizer": {"type": "SGD", "params": {"lr": 0.05}}, "steps_per_print": 1000,
+               "sequence_parallel_size": world, "zero_optimization": {"stage": 1}}
+        net = Net(sp_group=None)
+        net.load_state_dict(sd)
+        engine, _, _, _ = ds.initialize(model=net, config=cfg)
+        net.attn = DistributedAttention(core, groups._get_sequence_parallel_group(), scatter_idx=2, gather_idx=1)
+        lo, hi = rank * S // world, (rank + 1) * S // world
+        got = []
+        for _ in range(4):
+            l = engine(ids[:, lo:hi], labels[:, lo:hi]) / (2 * S) * world    # each rank holds 1/world of the tokens; dp averaging divides by world
+            engine.backward(l); engine.step()
+            t = l.detach().clone() / world; torch.distributed.all_reduce(t); got.append(round(float(t), 5))
+        return {"want": want, "got": got, "dp": engine.dp_world_size, "sp": engine.sequence_parallel_size}

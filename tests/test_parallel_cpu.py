@@ -143,3 +143,9 @@ def test_ccl_backend_host_collectives(world, simd, monkeypatch):
         if simd == "off":
             assert r["avx512"] == 0
     assert not os.path.exists("/dev/shm/" + res[0]["name"])
+
+
+def test_ulysses_training_through_the_engine_matches_full_sequence():
+    from tests.parallel_helper import ulysses_engine_worker
+    for r in run_distributed(ulysses_engine_worker, 2):
+        assert r["sp"] == 2 and r["got"] == pytest.approx(r["want"], rel=1e-5, abs=1e-5), r
