@@ -16,7 +16,6 @@ import socket
 from collections import Counter
 from typing import Dict, List, Optional
 
-import torch
 import torch.distributed as tdist
 
 from . import comm as _c

@@ -10,7 +10,6 @@ tp_parser :285, _replace :348, update_mp_params :447).
 """
 from __future__ import annotations
 
-import re
 from typing import Dict, List, Optional, Tuple
 
 import torch

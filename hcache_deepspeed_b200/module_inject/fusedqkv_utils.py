@@ -4,7 +4,7 @@ from __future__ import annotations
 
 import torch
 
-from .tp_shard import get_shard_size, get_shard_size_list
+from .tp_shard import get_shard_size_list
 
 FUSED_QKV_TYPES = {
     "CodeGenBlock": "codegentype", "BloomBlock": "bloomtype", "GLMBlock": "glmtype", "MPTBlock": "glmtype",

@@ -16,7 +16,7 @@ import torch
 import torch.nn.functional as F
 
 from .. import comm as dist
-from .tp_shard import get_shard_size, get_shard_size_list
+from .tp_shard import get_shard_size_list
 
 
 def _ws(group) -> int:

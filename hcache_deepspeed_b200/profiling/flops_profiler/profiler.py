@@ -8,7 +8,6 @@ not an ``nn.Module``) :func:`engine_flops` gives the analytical count of one for
 from __future__ import annotations
 
 import time
-from functools import partial
 from typing import Callable, Dict, List, Optional
 
 import torch

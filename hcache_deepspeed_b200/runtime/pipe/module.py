@@ -10,7 +10,6 @@ from __future__ import annotations
 
 import os
 import re
-from collections import defaultdict
 from functools import partial
 from typing import Callable, Iterable, List, Optional
 
