@@ -259,3 +259,38 @@ def test_restore_layer_ready_hook_streams_layers_in_order():
     a, _ = eng.put([1], [torch.tensor([5])])
     b, _ = eng.put([2], [torch.tensor([5])])
     torch.testing.assert_close(a, b, rtol=1e-4, atol=1e-4)
+
+
+def test_many_sessions_interleaved_turns_through_dram_and_nvme(tmp_path):
+    """Five conversations, three turns each in random order, a DRAM tier that holds about two saved states (the rest spill
+    to the NVMe tier and come back): every turn's first logits and greedy continuation equal those of an engine that never
+    dropped any KV cache."""
+    import random
+    eng, ref_eng = _engine(), _engine()
+    spec = eng.model().spec
+    for (n, t) in ref_eng.model().w.named_tensors().items():
+        t.copy_(eng.model().w.named_tensors()[n])
+    per_state = spec.n_layers * 40 * spec.hidden * 4          # fp32 hidden states of ~40 tokens
+    store = HiddenStateStore(dram_bytes=2 * per_state, nvme_dir=str(tmp_path))
+    mgr = HCacheSessionManager(eng, store, allow_recompute=False, allow_kv=False)
+    rng = random.Random(1)
+    g = torch.Generator().manual_seed(9)
+    order = [u for u in range(5) for _ in range(3)]
+    rng.shuffle(order)
+    lengths = {u: 0 for u in range(5)}
+    for uid in order:
+        prompt = torch.randint(0, spec.vocab, (rng.randint(5, 18), ), generator=g).to(torch.int32)
+        logits = mgr.prefill(uid, prompt)
+        ref_logits, _ = ref_eng.put([uid], [prompt], capture_latents=False)
+        torch.testing.assert_close(logits, ref_logits, rtol=2e-5, atol=2e-5)
+        gen = mgr.decode([uid], 3, logits)[0]
+        cur = ref_logits
+        for i, tok in enumerate(gen):
+            assert int(cur.argmax(-1)) == tok, (uid, i)
+            if i < len(gen) - 1:
+                cur, _ = ref_eng.put([uid], [torch.tensor([tok], dtype=torch.int32)], capture_latents=False)
+        lengths[uid] += int(prompt.numel()) + len(gen) - 1
+        st = mgr.end_turn(uid)
+        assert st.n_tokens == lengths[uid] and not mgr.is_resident(uid)
+    assert store.stats["saves"] == 15 and store.stats["spills"] > 0 and store.stats["nvme_loads"] > 0 and store.stats["dram_hits"] > 0
+    assert int(eng.free_blocks.min()) == int(_engine().free_blocks.min())        # every KV block went back to the pool
