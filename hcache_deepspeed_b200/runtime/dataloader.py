@@ -46,8 +46,11 @@ class DeepSpeedDataLoader:
         self.collate_fn = collate_fn
         self.pin_memory = pin_memory
         self.dataloader_drop_last = dataloader_drop_last
-        self.len = len(self.data_sampler) // batch_size if dataloader_drop_last else \
-            (len(self.data_sampler) + batch_size - 1) // batch_size
+        if self.curriculum_learning_enabled:
+            self.len = len(self.data_sampler) // max(1, batch_size * (data_parallel_world_size or 1))
+        else:
+            self.len = len(self.data_sampler) // batch_size if dataloader_drop_last else \
+                (len(self.data_sampler) + batch_size - 1) // batch_size
         self.batch_size = batch_size
         self.data = None
 
@@ -64,8 +67,13 @@ class DeepSpeedDataLoader:
         return next(self.data)
 
     def _create_dataloader(self):
-        kw = dict(batch_size=self.batch_size, pin_memory=self.pin_memory and torch.cuda.is_available(),
-                  sampler=self.data_sampler, num_workers=self.num_local_io_workers, drop_last=self.dataloader_drop_last)
+        if self.curriculum_learning_enabled:
+            # the data-efficiency sampler yields whole micro-batches of indices (ordered by the curriculum)
+            kw = dict(pin_memory=self.pin_memory and torch.cuda.is_available(), batch_sampler=self.data_sampler,
+                      num_workers=self.num_local_io_workers)
+        else:
+            kw = dict(batch_size=self.batch_size, pin_memory=self.pin_memory and torch.cuda.is_available(),
+                      sampler=self.data_sampler, num_workers=self.num_local_io_workers, drop_last=self.dataloader_drop_last)
         if self.collate_fn is not None:
             kw["collate_fn"] = self.collate_fn
         self.dataloader = DataLoader(self.dataset, **kw)

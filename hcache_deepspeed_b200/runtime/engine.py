@@ -471,7 +471,19 @@ class DeepSpeedEngine(torch.nn.Module):
             batch_size = self.train_micro_batch_size_per_gpu()
         dp_ws = self.dp_world_size
         dp_rank = dist.get_rank(group=self.data_parallel_group) if dist.is_initialized() else 0
+        loader_cfg = None
+        de = self._config.data_efficiency_config or {}
+        sampling = (de.get("data_sampling") or {}) if de.get("enabled", False) else {}
+        if route == "train" and data_sampler is None and sampling.get("enabled", False):
+            # data efficiency: curriculum-ordered sampling (ref: engine.py deepspeed_io + data_sampling/data_sampler.py)
+            from .data_pipeline.data_sampler import DeepSpeedDataSampler
+            data_sampler = DeepSpeedDataSampler(de, len(dataset), batch_size, dp_rank, dp_ws, self.data_parallel_group,
+                                                self.gradient_accumulation_steps(), self.global_rank,
+                                                drop_last=True)
+            self.training_data_sampler = data_sampler
+            loader_cfg = {"curriculum_learning_enabled": True}
         return DeepSpeedDataLoader(dataset=dataset, batch_size=batch_size, pin_memory=pin_memory,
+                                   deepspeed_dataloader_config=loader_cfg,
                                    collate_fn=collate_fn or self.collate_fn, local_rank=self.local_rank,
                                    tput_timer=self.tput_timer if route == "train" else None,
                                    num_local_io_workers=num_local_io_workers, data_sampler=data_sampler,
@@ -961,6 +973,7 @@ class DeepSpeedEngine(torch.nn.Module):
                      param_shapes=self.optimizer._param_shapes() if zero_wrapped else None,
                      frozen_param_shapes=frozen_shapes, frozen_param_fragments=frozen_fragments, shared_params=shared,
                      lr_scheduler=self.lr_scheduler.state_dict() if self.lr_scheduler is not None else None,
+                     data_sampler=self.training_data_sampler.state_dict() if getattr(self, "training_data_sampler", None) is not None else None,
                      skipped_steps=self.skipped_steps, global_steps=self.global_steps, global_samples=self.global_samples,
                      dp_world_size=self.dp_world_size, mp_world_size=self.mp_world_size,
                      ds_config=self._config._param_dict, ds_version=_version())
@@ -1098,6 +1111,8 @@ class DeepSpeedEngine(torch.nn.Module):
                 self.optimizer.refresh_fp32_params()
             if load_lr_scheduler_states and self.lr_scheduler is not None and ckpt.get("lr_scheduler") is not None:
                 self.lr_scheduler.load_state_dict(ckpt["lr_scheduler"])
+            if ckpt.get("data_sampler") is not None and getattr(self, "training_data_sampler", None) is not None:
+                self.training_data_sampler.load_state_dict(ckpt["data_sampler"])
         elif self.zero_optimization_stage() == 3:
             # module-only load under ZeRO-3: the trainable weights exist only as fp32 partitions in the optimizer shard
             zpath = self._get_zero_ckpt_name(load_dir, tag)
@@ -1108,7 +1123,7 @@ class DeepSpeedEngine(torch.nn.Module):
         elif hasattr(self.optimizer, "refresh_fp32_params"):
             self.optimizer.refresh_fp32_params()
         reserved = {"module", "buffer_names", "buffers", "optimizer", "param_shapes", "frozen_param_shapes",
-                    "frozen_param_fragments", "shared_params", "lr_scheduler", "skipped_steps",
+                    "frozen_param_fragments", "shared_params", "lr_scheduler", "skipped_steps", "data_sampler",
                     "global_steps", "global_samples", "dp_world_size", "mp_world_size", "ds_config", "ds_version"}
         client_state = {k: v for k, v in ckpt.items() if k not in reserved}
         return os.path.join(load_dir, str(tag)), client_state

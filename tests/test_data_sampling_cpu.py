@@ -202,3 +202,46 @@ def test_data_efficiency_config_tree_and_routing_helpers():
     b = BaseScheduler()
     b.state = {"schedule_type": "fixed_linear", "min_value": 16, "max_value": 128, "schedule_config": {"require_steps": 100, "seq_per_step": 16}}
     assert [b.get_value(s) for s in (0, 50, 1000)] == [16, 64, 128]
+
+
+def test_engine_builds_curriculum_sampler_from_data_efficiency_config(tmp_path):
+    """``initialize(training_data=...)`` with ``data_efficiency.data_sampling.curriculum_learning``: the engine's loader
+    feeds batches whose difficulty follows the schedule, and the sampler state rides in checkpoints (ref: engine.py
+    deepspeed_io, data_sampler.py state_dict)."""
+    import numpy as np
+    import torch
+    import hcache_deepspeed_b200 as ds
+
+    class DS(torch.utils.data.Dataset):
+        def __len__(self):
+            return 120
+
+        def __getitem__(self, i):
+            return torch.full((4, ), float(i % 10)), torch.tensor([float(i % 10)])
+
+    difficulty = np.arange(120) % 10            # the feature value IS the difficulty
+    cfg = {"train_micro_batch_size_per_gpu": 4, "optimizer": {"type": "SGD", "params": {"lr": 0.0}}, "steps_per_print": 1000,
+           "data_efficiency": {"enabled": True, "seed": 7, "data_sampling": {"enabled": True, "num_epochs": 1, "curriculum_learning": {
+               "enabled": True, "curriculum_metrics": {"len": {"min_difficulty": 1, "max_difficulty": 9, "schedule_type": "fixed_linear",
+                                                               "schedule_config": {"total_curriculum_step": 8, "difficulty_step": 1}}}}}}}
+    model = torch.nn.Linear(4, 1)
+    engine, _, loader, _ = ds.initialize(model=model, config=cfg, training_data=DS())
+    engine.training_data_sampler.difficulties["len"] = difficulty
+    it = iter(loader)
+    maxima = []
+    for step in range(8):
+        x, y = next(it)
+        assert x.shape == (4, 4)
+        maxima.append(float(x.max()))
+        loss = (engine(x) - y).pow(2).mean()
+        engine.backward(loss)
+        engine.step()
+        if step == 3:
+            engine.save_checkpoint(str(tmp_path), tag="c")
+            saved = dict(engine.training_data_sampler.state_dict())
+    assert maxima[0] <= 2 and maxima[-1] >= 5 and all(m <= 9 for m in maxima)          # easy samples first, harder later
+    assert maxima == sorted(maxima) or max(maxima[:3]) < max(maxima[5:])
+    engine2, _, loader2, _ = ds.initialize(model=torch.nn.Linear(4, 1), config=cfg, training_data=DS())
+    engine2.load_checkpoint(str(tmp_path), tag="c")
+    st = engine2.training_data_sampler.state_dict()
+    assert st["consumed_samples"] == saved["consumed_samples"] > 0 and st["curriculum_step"] == saved["curriculum_step"]
