@@ -438,6 +438,8 @@ class DeepSpeedEngine(torch.nn.Module):
                                             immediate_grad_update=self._config.bf16_config.immediate_grad_update)
         else:
             self.optimizer = basic
+        for p in self.module.parameters():          # utils.safe_get_full_fp32_param & co find their optimizer through this
+            p._ds_optimizer = self.optimizer
         log_dist(f"DeepSpeed optimizer = {type(self.optimizer).__name__} over {type(basic).__name__}", ranks=[0])
 
     def _configure_lr_scheduler(self, client_lr_scheduler):

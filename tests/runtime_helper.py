@@ -634,3 +634,63 @@ def partition_activations_worker(rank, world):
     checkpointing.configure(None, partition_activations=False, checkpoint_in_cpu=False)
     checkpointing.reset()
     return out
+
+
+def safe_accessors_worker(rank, world, stage):
+    """``deepspeed.utils.safe_get_* / safe_set_*`` under ZeRO 1 / 2 / 3: full fp32 parameter, gradient (between backward
+    and step) and Adam state of a partitioned parameter, setters that every rank sees afterwards, and the partition-local
+    variants of ZeRO-3 (ref: utils/tensor_fragment.py:118-330)."""
+    import hcache_deepspeed_b200 as ds
+    from hcache_deepspeed_b200 import utils as U
+    ds.init_distributed(dist_backend="gloo")
+    torch.manual_seed(0)
+    model = TinyNet(32)
+    ref = TinyNet(32)
+    ref.load_state_dict(model.state_dict())
+    cfg = {"train_micro_batch_size_per_gpu": 4, "optimizer": {"type": "Adam", "params": {"lr": 1e-2}}, "steps_per_print": 1000,
+           "zero_optimization": {"stage": stage, "stage3_param_persistence_threshold": 0}}
+    engine, _, _, _ = ds.initialize(model=model, config=cfg)
+    opt_ref = torch.optim.Adam(ref.parameters(), lr=1e-2)
+    x, y = next(iter(make_batches(1, 4 * world, 32)))
+    lo = rank * 4
+    # reference: the averaged gradient of the global batch
+    (sum(ref(x[r * 4:r * 4 + 4], y[r * 4:r * 4 + 4]) for r in range(world)) / world).backward()
+    want_grad = {n: p.grad.clone() for n, p in ref.named_parameters()}
+    loss = engine(x[lo:lo + 4], y[lo:lo + 4])
+    engine.backward(loss)
+    out = {}
+    def is_matrix(q):
+        return len(getattr(q, "ds_shape", q.shape)) == 2
+
+    name, p = next((n, q) for n, q in engine.module.named_parameters() if is_matrix(q))
+    g = U.safe_get_full_grad(p)
+    out["grad_err"] = float((g - want_grad[name]).abs().max())
+    U.safe_set_full_grad(p, torch.zeros_like(want_grad[name]))          # freeze this parameter for one step
+    before = U.safe_get_full_fp32_param(p).clone()
+    engine.step()
+    after = U.safe_get_full_fp32_param(p)
+    out["frozen_by_zero_grad"] = float((after - before).abs().max())
+    other_name, other = next((n, q) for n, q in engine.module.named_parameters() if is_matrix(q) and q is not p)
+    opt_ref.step()
+    out["other_param_err"] = float((U.safe_get_full_fp32_param(other) - dict(ref.named_parameters())[other_name].detach()).abs().max())
+    ea = U.safe_get_full_optimizer_state(other, "exp_avg")
+    out["exp_avg_err"] = float((ea - opt_ref.state[dict(ref.named_parameters())[other_name]]["exp_avg"]).abs().max())
+    # setters: a new value set collectively is what every rank reads back, and what the next forward uses
+    new = torch.full(tuple(after.shape), 0.25)
+    U.safe_set_full_fp32_param(p, new)
+    U.safe_set_full_optimizer_state(p, torch.ones_like(new), "exp_avg")
+    out["set_param"] = float((U.safe_get_full_fp32_param(p) - new).abs().max())
+    out["set_state"] = float((U.safe_get_full_optimizer_state(p, "exp_avg") - 1.0).abs().max())
+    if stage == 3:
+        from hcache_deepspeed_b200.runtime.zero import GatheredParameters
+        with GatheredParameters([p]):
+            out["lp_follows"] = float((p.data.float() - 0.25).abs().max())
+        loc = U.safe_get_local_fp32_param(p)
+        out["local_numel"] = (int(loc.numel()), int(p.ds_partition_numel))
+        U.safe_set_local_fp32_param(p, torch.full_like(loc, float(rank + 1)))
+        full = U.safe_get_full_fp32_param(p).reshape(-1)
+        out["local_set"] = (float(full[0]), float(full[-1]))
+        out["local_state"] = int(U.safe_get_local_optimizer_state(p, "exp_avg").numel())
+    else:
+        out["lp_follows"] = float((p.data.float() - 0.25).abs().max())
+    return out

@@ -576,3 +576,14 @@ def test_partition_activations_across_model_parallel_ranks():
         for k, v in r.items():
             assert v["err"] < 1e-6 and v["loss"] < 1e-6, (k, v)
             assert v["saved"] and all(part * 2 == full for full, part in v["saved"]), (k, v)      # half of each input kept per rank
+
+
+@pytest.mark.parametrize("stage", [1, 2, 3])
+def test_safe_accessors_of_partitioned_tensors_2ranks(stage):
+    from tests.runtime_helper import safe_accessors_worker
+    for r in run_distributed(safe_accessors_worker, 2, stage):
+        assert r["grad_err"] < 1e-6 and r["frozen_by_zero_grad"] == 0.0, r
+        assert r["other_param_err"] < 1e-6 and r["exp_avg_err"] < 1e-7, r
+        assert r["set_param"] == 0.0 and r["set_state"] == 0.0 and r["lp_follows"] == 0.0, r
+        if stage == 3:
+            assert r["local_numel"][0] == r["local_numel"][1] and r["local_set"] == (1.0, 2.0) and r["local_state"] == r["local_numel"][0]
