@@ -86,6 +86,7 @@ _LAZY_MODULES = {
     "compression": ".compression", "autotuning": ".autotuning", "elasticity": ".elasticity", "launcher": ".launcher",
     "monitor": ".monitor", "profiling": ".profiling", "accelerator": ".accelerator", "linear": ".linear", "nvme": ".nvme",
     "model_implementations": ".model_implementations", "checkpointing": ".runtime.activation_checkpointing.checkpointing",
+    "domino": ".runtime.domino", "comm": ".comm", "compile": ".compile",
 }
 _LAZY_ATTRS = {
     "DeepSpeedEngine": (".runtime.engine", "DeepSpeedEngine"), "DeepSpeedConfig": (".runtime.config", "DeepSpeedConfig"),
@@ -98,6 +99,13 @@ _LAZY_ATTRS = {
     "DeepSpeedTransformerConfig": (".ops.transformer.transformer", "DeepSpeedTransformerConfig"),
     "OnDevice": (".utils.init_on_device", "OnDevice"), "tp_model_init": (".runtime.tensor_parallel.tp_manager", "tp_model_init"),
     "get_accelerator": (".accelerator", "get_accelerator"),
+    "DeepSpeedConfigError": (".runtime.config", "DeepSpeedConfigError"), "ADAM_OPTIMIZER": (".runtime.config", "ADAM_OPTIMIZER"),
+    "LAMB_OPTIMIZER": (".runtime.config", "LAMB_OPTIMIZER"), "add_tuning_arguments": (".runtime.lr_schedules", "add_tuning_arguments"),
+    "replace_transformer_layer": (".module_inject.replace_module", "replace_transformer_layer"),
+    "revert_transformer_layer": (".module_inject.replace_module", "revert_transformer_layer"),
+    "set_autotp_mode": (".runtime.tensor_parallel", "set_autotp_mode"),
+    "git_hash": (".git_version_info", "git_hash"), "git_branch": (".git_version_info", "git_branch"),
+    "TORCH_DISTRIBUTED_DEFAULT_PORT": (".constants", "TORCH_DISTRIBUTED_DEFAULT_PORT"),
 }
 
 

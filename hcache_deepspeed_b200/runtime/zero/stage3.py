@@ -608,3 +608,25 @@ def estimate_zero3_model_states_mem_needs(total_params, largest_layer_params, nu
         cpu_mem = largest_layer_params * 4 * num_gpus_per_node * additional_buffer_factor if zero_init else \
             total_params * 4 * num_gpus_per_node * additional_buffer_factor
     return int(cpu_mem), int(gpu_mem), largest_layer_memory
+
+
+import contextlib
+
+
+@contextlib.contextmanager
+def unwrap_model_for_generation(model):
+    """ZeRO-3 engines: gather every parameter ONCE and take the fetch / release hooks off for the duration, so a
+    ``generate`` loop does not all-gather each layer at every token (ref: stage3.py:77-106). ``model`` is the engine."""
+    from .partition_parameters import GatheredParameters
+    opt = getattr(model, "optimizer", None)
+    offload = getattr(opt, "parameter_offload", None)
+    module = getattr(model, "module", model)
+    with GatheredParameters(list(module.parameters())):
+        if offload is not None:
+            offload.destroy()
+        try:
+            yield model
+        finally:
+            if offload is not None:
+                offload._install(offload.module)
+                offload.reset_trace()

@@ -587,3 +587,41 @@ def test_safe_accessors_of_partitioned_tensors_2ranks(stage):
         assert r["set_param"] == 0.0 and r["set_state"] == 0.0 and r["lp_follows"] == 0.0, r
         if stage == 3:
             assert r["local_numel"][0] == r["local_numel"][1] and r["local_set"] == (1.0, 2.0) and r["local_state"] == r["local_numel"][0]
+
+
+def test_unwrap_model_for_generation_gathers_once():
+    """``zero.unwrap_model_for_generation(engine)``: inside, every ZeRO-3 parameter is resident and forwards trigger no
+    fetch / release; afterwards the hooks are back and training continues."""
+    import hcache_deepspeed_b200 as ds
+    from hcache_deepspeed_b200.runtime.zero import ZeroParamStatus, unwrap_model_for_generation
+    from hcache_deepspeed_b200.runtime.zero import partition_parameters as PP
+    torch.manual_seed(0)
+    model = torch.nn.Sequential(torch.nn.Linear(8, 16), torch.nn.Tanh(), torch.nn.Linear(16, 1))
+    engine, _, _, _ = ds.initialize(model=model, config={
+        "train_micro_batch_size_per_gpu": 2, "optimizer": {"type": "SGD", "params": {"lr": 0.1}}, "steps_per_print": 1000,
+        "zero_optimization": {"stage": 3, "stage3_param_persistence_threshold": 0}})
+    x = torch.randn(2, 8)
+    want = engine(x).detach().clone()
+    assert all(p.ds_status == ZeroParamStatus.NOT_AVAILABLE for p in model.parameters())
+    calls = {"n": 0}
+    orig = PP.all_gather_params
+
+    def counting(params, async_op=False):
+        calls["n"] += sum(1 for p in params if PP.is_zero_param(p) and p.ds_status != ZeroParamStatus.AVAILABLE)
+        return orig(params, async_op=async_op)
+
+    with unwrap_model_for_generation(engine):
+        PP.all_gather_params = counting
+        try:
+            assert all(p.ds_status == ZeroParamStatus.AVAILABLE for p in model.parameters())
+            with torch.no_grad():
+                for _ in range(3):
+                    torch.testing.assert_close(model(x), want)
+        finally:
+            PP.all_gather_params = orig
+        assert calls["n"] == 0 and all(p.ds_status == ZeroParamStatus.AVAILABLE for p in model.parameters())
+    assert all(p.ds_status == ZeroParamStatus.NOT_AVAILABLE for p in model.parameters())
+    loss = engine(x).pow(2).mean()
+    engine.backward(loss)
+    engine.step()
+    assert float((engine(x).detach() - want).abs().max()) > 0
