@@ -95,3 +95,16 @@ class DeepSpeedCheckpoint:
         for f in self.file_list:
             if not os.path.isfile(f):
                 raise FileNotFoundError(f"{f} is not existent")
+
+
+# ---- file names of one rank's pieces of a checkpoint (ref: checkpoint/utils.py:11-37) ---------------------------------
+def get_model_ckpt_name_for_rank(base_folder: str, mp_rank_str: str) -> str:
+    return os.path.join(base_folder, f"mp_rank_{mp_rank_str}_model_states.pt")
+
+
+def get_zero_ckpt_name_for_rank(base_folder: str, dp_rank: int, mp_rank: int) -> str:
+    return os.path.join(base_folder, f"zero_pp_rank_{dp_rank}_mp_rank_{mp_rank:02d}_optim_states.pt")
+
+
+def get_layer_ckpt_name_for_rank(base_folder: str, layer_id: str, tp_rank: int) -> str:
+    return os.path.join(base_folder, f"{layer_id}-model_{tp_rank:02d}-model_states.pt")

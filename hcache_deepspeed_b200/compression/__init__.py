@@ -2,3 +2,4 @@
 activation quantisation and layer reduction, driven by the ``compression_training`` config section."""
 from .compress import init_compression, redundancy_clean  # noqa: F401
 from .scheduler import compression_scheduler  # noqa: F401
+from .helper import convert_conv1d_to_linear  # noqa: F401

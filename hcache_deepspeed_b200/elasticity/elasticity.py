@@ -182,3 +182,31 @@ def compute_elastic_config(ds_config: dict, target_deepspeed_version: str = "0.1
     if return_microbatch:
         return final_bs, valid_gpus, micro_batch
     return final_bs, valid_gpus
+
+
+def ensure_immutable_elastic_config(runtime_elastic_config_dict: dict) -> None:
+    """The resource scheduler publishes the elastic config it planned with in ``DEEPSPEED_ELASTICITY_CONFIG``; a runtime
+    config that disagrees on batch size, micro batches or version is an error (ref: elasticity.py:208-231)."""
+    import json
+    from ..utils.logging import logger
+    from .constants import DEEPSPEED_ELASTICITY_CONFIG
+    raw = os.environ.get(DEEPSPEED_ELASTICITY_CONFIG)
+    if raw is None:
+        logger.warning("DEEPSPEED_ELASTICITY_CONFIG is not set: cannot check that the resource scheduler scales this job over "
+                       "compatible GPU counts")
+        return
+    sched, run = ElasticityConfig(json.loads(raw)), ElasticityConfig(runtime_elastic_config_dict)
+    for field in ("max_acceptable_batch_size", "micro_batches", "version"):
+        if getattr(sched, field) != getattr(run, field):
+            raise ElasticityConfigError(f"elastic config seen by the resource scheduler ({field}={getattr(sched, field)}) does not "
+                                        f"match the runtime config ({field}={getattr(run, field)})")
+
+
+def is_torch_elastic_compatible() -> bool:
+    """torch.distributed.elastic (the agent ``elasticity/elastic_agent.py`` builds on) exists since torch 1.11."""
+    import torch
+    try:
+        major, minor = (int(x) for x in torch.__version__.split(".")[:2])
+    except ValueError:
+        return True
+    return (major, minor) >= (1, 11)

@@ -176,6 +176,20 @@ MODEL_TYPE_TO_POLICY = {
 
 __all__ = ["InferenceV2Policy", "POLICIES", "MODEL_TYPE_TO_POLICY", "supported_model_types"] + [c.__name__ for c in set(MODEL_TYPE_TO_POLICY.values())]
 
+_LAZY = {"DSInferenceModelBase": ".inference_model_base", "DSTransformerModelBase": ".inference_model_base",
+         "DSMoETransformerModelBase": ".inference_model_base", "ContainerMap": ".inference_policy_base",
+         "LayerContainer": ".layer_container_base"}
+
+
+def __getattr__(name):
+    if name in _LAZY:
+        import importlib
+        value = getattr(importlib.import_module(_LAZY[name], __name__), name)
+        globals()[name] = value
+        return value
+    raise AttributeError(f"module {__name__!r} has no attribute {name!r}")
+
+
 # the reference's per-family import paths (llama_v2.policy, opt.model, ...) resolve through one table: family_paths.py
 from . import family_paths as _family_paths  # noqa: E402
 
