@@ -9,6 +9,7 @@ move), and the schedule is written back into the hook installer and the optimize
 their own streams; launch-bound regions are CUDA-graphed elsewhere."""
 from __future__ import annotations
 
+import time
 from typing import Callable, Dict, List, Optional
 
 import torch
@@ -26,6 +27,8 @@ from .trace import ModuleTrace
 
 # name -> pass(ctx) ; user passes can be added with register_compile_pass
 opt_passes: Dict[str, Callable] = {}
+# (pass name, seconds) of every pass run so far - what ``engine.get_compile_time()`` returns (ref: compile/backend.py)
+opt_pass_times: List[tuple] = []
 
 
 def register_compile_pass(name: str, fn: Callable) -> None:
@@ -99,7 +102,9 @@ def launch_compile_passes(offload, optimizer=None, config: Optional[CompileConfi
     """Run ``passes`` (default: all ZeRO-3 ones, selective gather first so prefetch skips what became resident)."""
     ctx = CompileContext(offload, optimizer, config or CompileConfig(deepcompile=True), group)
     for name in passes or DEFAULT_Z3_PASSES:
+        t0 = time.perf_counter()
         opt_passes[name](ctx)
+        opt_pass_times.append((name, time.perf_counter() - t0))
     if ctx.config.debug_log:
         log_dist("schedule compiler:\n" + ctx.trace.summary() + f"\n{ctx.report}", [0])
     return ctx.report

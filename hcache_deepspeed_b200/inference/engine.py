@@ -57,6 +57,7 @@ class InferenceEngine(torch.nn.Module):
         self.mpu = config.tensor_parallel.mpu
         self.model_profile_enabled = False
         self._model_times: List[float] = []
+        self._is_compiled = False
         self._cuda_graph = None
         self._graph_inputs = None
         self._graph_output = None
@@ -300,6 +301,73 @@ class InferenceEngine(torch.nn.Module):
             else:
                 self._model_times.append((time.perf_counter() - t0) * 1e3)
         return out
+
+    # ---- model-specific fix-ups under tensor parallelism (ref: engine.py:207-228) ------------------------------------
+    def _tp_rank_size(self):
+        tp = self._config.tensor_parallel.tp_size
+        rank = torch.distributed.get_rank(self.inference_mp_group) if tp > 1 and self.inference_mp_group is not None else 0
+        return rank, tp
+
+    def remove_mask_prepare_for_bloom(self) -> None:
+        """Older BLOOM implementations expand the attention mask in ``_prepare_attn_mask``; the fused path wants it as given."""
+        tr = getattr(self.module, "transformer", None)
+        if tr is not None and hasattr(tr, "_prepare_attn_mask"):
+            tr._prepare_attn_mask = lambda attention_mask, *args, **kwargs: attention_mask
+
+    def build_alibi_tensor(self) -> None:
+        """Make the model's ALiBi builders return this rank's heads only: BLOOM (``build_alibi_tensor``), MPT
+        (``build_mpt_alibi_tensor``) and Baichuan-style (``get_alibi_mask``) layouts."""
+        from ..module_inject.auto_tp_model_utils import build_bloom_alibi_tensor, slice_heads
+        rank, tp = self._tp_rank_size()
+        tr = getattr(self.module, "transformer", None)
+        if tr is not None and hasattr(tr, "build_alibi_tensor"):
+            tr.build_alibi_tensor = lambda attention_mask, num_heads, dtype: build_bloom_alibi_tensor(
+                attention_mask, num_heads, dtype, mp_size=tp, mp_rank=rank)
+        if tr is not None and hasattr(tr, "build_mpt_alibi_tensor") and not hasattr(tr, "build_mpt_alibi_tensor_orig"):
+            tr.build_mpt_alibi_tensor_orig = tr.build_mpt_alibi_tensor
+            tr.build_mpt_alibi_tensor = lambda *a, **k: slice_heads(tr.build_mpt_alibi_tensor_orig(*a, **k), 1, rank, tp)
+        inner = getattr(self.module, "model", None)
+        if inner is not None and hasattr(inner, "get_alibi_mask") and not hasattr(inner, "get_alibi_mask_orig"):
+            inner.get_alibi_mask_orig = inner.get_alibi_mask
+            inner.get_alibi_mask = lambda *a, **k: slice_heads(inner.get_alibi_mask_orig(*a, **k), 0, rank, tp)
+
+    def build_attn_bias(self) -> None:
+        """MPT builds one attention bias ``[1, heads, 1, seq]`` for all heads: keep this rank's heads."""
+        from ..module_inject.auto_tp_model_utils import slice_heads
+        rank, tp = self._tp_rank_size()
+        tr = getattr(self.module, "transformer", None)
+        if tr is not None and hasattr(tr, "_attn_bias") and not hasattr(tr, "_attn_bias_orig"):
+            tr._attn_bias_orig = tr._attn_bias
+
+            def sliced(*a, **k):
+                bias, mask = tr._attn_bias_orig(*a, **k)
+                return (slice_heads(bias, 1, rank, tp) if bias is not None else None), mask
+
+            tr._attn_bias = sliced
+
+    def load_model_with_checkpoint(self, r_module: Optional[torch.nn.Module] = None) -> None:
+        """Fill ``r_module`` (default: the wrapped module; may be on the meta device) from the checkpoint description given
+        at ``init_inference(checkpoint=...)``, slicing to this tensor-parallel rank (ref: engine.py:301-380)."""
+        from ..module_inject.load_checkpoint import load_checkpoint_into
+        if self._config.checkpoint is None:
+            raise ValueError("load_model_with_checkpoint needs init_inference(..., checkpoint=<json | dir>)")
+        rank, tp = self._tp_rank_size()
+        load_checkpoint_into(r_module if r_module is not None else self.module, self._config.checkpoint,
+                             self._config.base_dir or "", tp_size=tp, tp_rank=rank, strict=False)
+
+    def compile(self, backend=None, compile_kwargs=None) -> None:
+        """The reference hands the module to ``torch.compile`` (engine.py:608). Here the launch-bound decode loop is
+        removed by CUDA-graph capture instead: after this call the un-injected module's forward is captured on its first
+        GPU call and replayed afterwards (the injected path already runs graph-captured steps)."""
+        if self._is_compiled:
+            return
+        if self._config.tensor_parallel.tp_size == 1:
+            self._config.enable_cuda_graph = True
+        self._is_compiled = True
+
+    @property
+    def is_compiled(self) -> bool:
+        return self._is_compiled
 
     # ---- CUDA graph for the un-injected module (ref: engine.py:494-520) ------------------------------------
     def _create_cuda_graph(self, *inputs, **kwargs):

@@ -138,6 +138,20 @@ class BlockedKVCache:
         host.copy_(sel)
         return host
 
+    # ---- block bookkeeping (the allocator belongs to the state manager, which binds it here; ref: kv_cache.py:144-201) ------
+    def bind_allocator(self, allocator) -> None:
+        self._allocator = allocator
+
+    def reserve(self, num_blocks: int, cache_group: int = 0) -> torch.Tensor:
+        return self._allocator.allocate(num_blocks)
+
+    def free(self, blocks: Iterable[int], cache_group: int = 0) -> None:
+        self._allocator.free(blocks if isinstance(blocks, torch.Tensor) else torch.as_tensor(list(blocks), dtype=torch.int32))
+
+    @property
+    def free_blocks(self):
+        return [self._allocator.free_blocks]
+
     def restore(self, blocks: Iterable[int], host_in: torch.Tensor) -> None:
         """Inverse of :meth:`offload` into (possibly different) block ids."""
         ids = torch.as_tensor(list(blocks) if not isinstance(blocks, torch.Tensor) else blocks, dtype=torch.int32)

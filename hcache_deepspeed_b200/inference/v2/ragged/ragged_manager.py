@@ -27,6 +27,7 @@ class DSStateManager:
         self._kv_cache = BlockedKVCache(kv_configs, config.memory_config, mp_group=base_mp_group, offload=config.offload,
                                         device=device)
         self._allocator = BlockedAllocator(self._kv_cache.num_blocks)
+        self._kv_cache.bind_allocator(self._allocator)
 
     # ---- sequences --------------------------------------------------------------------------------
     def get_sequence(self, uid: int) -> Optional[DSSequenceDescriptor]:
@@ -92,6 +93,39 @@ class DSStateManager:
     @property
     def kv_cache(self) -> BlockedKVCache:
         return self._kv_cache
+
+    def restore_kv(self, uid: int, latent, qk_layer, qk_w, b=None, start: int = 0) -> int:
+        """Rebuild a sequence's K/V pages from saved per-layer hidden states with a caller-supplied projection.
+
+        ``latent[l]`` is ``[tokens, hidden]`` for layer ``l``; ``qk_layer(latent_l, qk_w[l], b=bias)`` returns that layer's
+        ``[tokens, 2 * kv_heads * head_dim]`` (K then V; positional encoding already applied). Pages are allocated as needed
+        and the sequence's seen-token count advanced. This is the model-agnostic slow path; the model's own ``restore_kv``
+        (models/transformer.py) is the pipelined one the engine uses. The reference has this method as an unfinished stub
+        (ragged_manager.py:170) - here it does what its signature says. Returns the number of tokens restored.
+        """
+        seq = self.get_or_create_sequence(uid)
+        n_tok = int(latent[0].shape[0])
+        bs = self.kv_block_size
+        need = -(-(start + n_tok) // bs) - seq.cur_allocated_blocks
+        if need > 0:
+            seq.extend_kv_cache(self._allocator.allocate(need))
+        ids = seq.all_block_ids.to(torch.long)
+        pos = torch.arange(start, start + n_tok)
+        blk, off = ids[pos // bs], pos % bs
+        for layer_id, latent_layer in enumerate(latent):
+            cache = self.get_cache(layer_id)                      # [blocks, 2, heads, block_size, head_dim]
+            w = qk_w[layer_id] if isinstance(qk_w, (list, tuple)) else qk_w
+            bias = b[layer_id] if isinstance(b, (list, tuple)) else b
+            kv = qk_layer(latent_layer.to(cache.device), w, b=bias)
+            heads, hd = cache.shape[2], cache.shape[4]
+            kv = kv.reshape(n_tok, 2, heads, hd).to(cache.dtype)
+            dblk, doff = blk.to(cache.device), off.to(cache.device)
+            cache[dblk, 0, :, doff] = kv[:, 0]
+            cache[dblk, 1, :, doff] = kv[:, 1]
+        if start + n_tok > seq.seen_tokens:
+            seq.pre_forward(start + n_tok - seq.seen_tokens)
+            seq.post_forward()
+        return n_tok
 
     # ---- whole-sequence KV offload (plain KV offload path) --------------------------------------------
     def offload_sequence(self, uid: int) -> torch.Tensor:

@@ -213,6 +213,26 @@ class RaggedBatchWrapper:
     # name kept for code written against the reference (engine_v2.py:173)
     _inflight_seq_descriptors_shadow = inflight_seq_descriptors_shadow
 
+    # ---- accessors of the reference's wrapper, expressed over this wrapper's staging layout (ragged_wrapper.py:230-276) ----
+    def inflight_seq_descriptors(self, on_device: bool = True) -> torch.Tensor:
+        """int32 ``[n_seqs, 4]``: (first token of the sequence in the batch, tokens in flight, tokens seen before, 0)."""
+        rows = [(b, n, seen, 0) for b, n, seen in self._inflight] or [(0, 0, 0, 0)][:0]
+        t = torch.tensor(rows, dtype=torch.int32).reshape(-1, 4)
+        return t.to(self._device) if on_device and self._device.type != "cpu" else t
+
+    def batch_metadata_buffer(self, on_device: bool = True) -> torch.Tensor:
+        """int32 ``[2]``: (tokens, sequences) of the in-flight batch."""
+        t = torch.tensor([self._n_tokens, self._n_seqs], dtype=torch.int32)
+        return t.to(self._device) if on_device and self._device.type != "cpu" else t
+
+    def kv_ptrs(self, on_device: bool = True) -> torch.Tensor:
+        """Where each sequence's KV block ids live: here the rows of the block table (``block_tables()``), not raw pointers."""
+        return self._view("tables", self._n_seqs * self._stride, on_device).view(self._n_seqs, self._stride)
+
+    def masks(self, on_device: bool = True):
+        """Placeholder of the reference for non-causal masks (BERT-like models): not supported there either."""
+        return None
+
     @property
     def sequences(self) -> List[DSSequenceDescriptor]:
         return self._descs

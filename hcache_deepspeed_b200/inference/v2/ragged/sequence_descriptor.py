@@ -58,6 +58,11 @@ class DSSequenceDescriptor(BaseSequenceDescriptor):
         #: set while the sequence's KV lives in host memory (whole-sequence KV offload)
         self.offloaded_kv: Optional[torch.Tensor] = None
 
+    @property
+    def max_context(self) -> int:
+        """Tokens this sequence's block table can address (blocks x block size is the engine's business; here: blocks)."""
+        return self._max_blocks
+
     # ---- token accounting -------------------------------------------------------------------
     @property
     def seen_tokens(self) -> int:

@@ -39,18 +39,33 @@ def build_bloom_alibi_tensor(attention_mask: torch.Tensor, num_heads: int, dtype
     return alibi.reshape(batch * num_heads, 1, seq).to(dtype)
 
 
+def slice_heads(t: torch.Tensor, dim: int, rank: int, world: int) -> torch.Tensor:
+    """This rank's heads along ``dim`` of a per-head tensor (same uneven split as the attention sharding)."""
+    if t is None or world <= 1:
+        return t
+    from .tp_shard import get_shard_size_list
+    sizes = get_shard_size_list(t.shape[dim], world)
+    return t.narrow(dim, sum(sizes[:rank]), sizes[rank])
+
+
+def _world():
+    return (dist.get_rank(), dist.get_world_size()) if dist.is_initialized() else (0, 1)
+
+
 def get_alibi_mask(self, tensor, seq_length_with_past):
-    """Baichuan-style cached ALiBi mask, sliced to this rank's heads."""
-    mask = self._get_alibi_mask_orig(tensor, seq_length_with_past) if hasattr(self, "_get_alibi_mask_orig") else None
-    if mask is not None and dist.is_initialized() and dist.get_world_size() > 1:
-        per = mask.shape[0] // dist.get_world_size()
-        mask = mask[dist.get_rank() * per:(dist.get_rank() + 1) * per]
-    return mask
+    """Baichuan-style cached ALiBi mask ``[heads, seq, seq]``, sliced to this rank's heads; installed as the class's
+    ``get_alibi_mask`` with the original kept as ``get_alibi_mask_orig`` (ref: auto_tp_model_utils.py:63)."""
+    mask = self.get_alibi_mask_orig(tensor, seq_length_with_past)
+    return slice_heads(mask, 0, *_world())
 
 
 def build_mpt_alibi_tensor(self, *args, **kwargs):
-    alibi = self.build_mpt_alibi_tensor_orig(*args, **kwargs)
-    if dist.is_initialized() and dist.get_world_size() > 1:
-        per = alibi.shape[1] // dist.get_world_size()
-        alibi = alibi[:, dist.get_rank() * per:(dist.get_rank() + 1) * per]
-    return alibi
+    """MPT's ``[1, heads, 1, seq]`` ALiBi tensor for this rank's heads (original kept as ``build_mpt_alibi_tensor_orig``)."""
+    return slice_heads(self.build_mpt_alibi_tensor_orig(*args, **kwargs), 1, *_world())
+
+
+def build_mpt_atten_bias_tensor(self, device, dtype, attention_mask=None, prefix_mask=None, sequence_id=None):
+    """MPT's ``_attn_bias`` for this rank's heads (original kept as ``_attn_bias_orig``)."""
+    bias, mask = self._attn_bias_orig(device, dtype, attention_mask=attention_mask, prefix_mask=prefix_mask,
+                                      sequence_id=sequence_id)
+    return (slice_heads(bias, 1, *_world()) if bias is not None else None), mask

@@ -9,6 +9,7 @@ topkgating :374, TopKGate :449, MOELayer :533).
 from __future__ import annotations
 
 import math
+import time
 from typing import Callable, Optional, Tuple
 
 import torch
@@ -239,28 +240,48 @@ class MOELayer(torch.nn.Module):
         self.ep_size, self.ep_group_name, self.num_local_experts = ep_size, ep_group_name, num_local_experts
         self.l_aux, self.exp_counts = None, None
         self.wall_clock_breakdown = False
+        self.gate_time = self.time_falltoall = self.time_salltoall = self.time_moe = 0.0   # ms, of the last forward
 
     def _set_ep_group(self, ep_group):
         self.ep_group = ep_group
         self.gate._set_ep_group(ep_group)
 
+    def _now(self, x: Tensor) -> float:
+        """Wall clock in ms for the ``wall_clock_breakdown`` counters (the device is drained first so spans are real)."""
+        if x.is_cuda:
+            torch.cuda.synchronize(x.device)
+        return time.perf_counter() * 1e3
+
     def forward(self, *inputs: Tensor, **kwargs) -> Tensor:
         x = inputs[0]
+        timed = self.wall_clock_breakdown
         d_model = x.shape[-1]
         tokens = x.reshape(-1, d_model)
+        t0 = self._now(x) if timed else 0.0
         self.l_aux, combine, dispatch, self.exp_counts = self.gate(tokens, inputs[1] if len(inputs) > 1 else None)
+        if timed:
+            t1 = self._now(x)
+            self.gate_time = t1 - t0
         dispatched = torch.einsum("sec,sm->ecm", dispatch.type_as(x), tokens)
         tp = groups._get_model_parallel_world_size() if groups.mpu is not None else 1
         if tp > 1:
             dispatched = drop_tokens(dispatched, dim=1)
+        ta = self._now(x) if timed else 0.0
         if self.ep_size > 1:
             dispatched = _AllToAll.apply(self.ep_group, dispatched)
+        if timed:
+            self.time_falltoall = self._now(x) - ta
         dispatched = dispatched.reshape(self.ep_size, self.num_local_experts, -1, d_model)
         out = self.experts(dispatched)
         out = out.reshape(self.ep_size * self.num_local_experts, -1, d_model)
+        ta = self._now(x) if timed else 0.0
         if self.ep_size > 1:
             out = _AllToAll.apply(self.ep_group, out)
+        if timed:
+            self.time_salltoall = self._now(x) - ta
         if tp > 1:
             out = gather_tokens(out, dim=1)
         combined = torch.einsum("sec,ecm->sm", combine.type_as(x), out)
+        if timed:
+            self.time_moe = self._now(x) - t0
         return combined.reshape(x.shape)

@@ -28,6 +28,7 @@ from .checkpoint_engine import NebulaCheckpointEngine, TorchCheckpointEngine
 from .config import (ADAGRAD_OPTIMIZER, ADAM_OPTIMIZER, ADAMW_OPTIMIZER, LAMB_OPTIMIZER, LION_OPTIMIZER,
                      ONEBIT_ADAM_OPTIMIZER, ONEBIT_LAMB_OPTIMIZER, SGD_OPTIMIZER, ZERO_ONE_ADAM_OPTIMIZER, DeepSpeedConfig)
 from .dataloader import DeepSpeedDataLoader
+from .engine_accessors import EngineAccessors
 from .fp16.fused_optimizer import FP16_Optimizer, FP16_UnfusedOptimizer
 from .utils import clip_grad_norm_, flatten_dense_tensors, get_grad_norm, unflatten_dense_tensors
 from .zero.stage3 import DeepSpeedZeroOptimizer_Stage3
@@ -56,7 +57,7 @@ def _device_for(local_rank: int) -> torch.device:
     return torch.device("cpu")
 
 
-class DeepSpeedEngine(torch.nn.Module):
+class DeepSpeedEngine(EngineAccessors, torch.nn.Module):
 
     def __init__(self, args=None, model: torch.nn.Module = None, optimizer=None, model_parameters=None, training_data=None,
                  lr_scheduler=None, mpu=None, dist_init_required: Optional[bool] = None, collate_fn=None, config=None,
@@ -158,6 +159,14 @@ class DeepSpeedEngine(torch.nn.Module):
             from .progressive_layer_drop import ProgressiveLayerDrop
             self.progressive_layer_drop = ProgressiveLayerDrop(theta=self._config.pld_config.theta,
                                                                gamma=self._config.pld_config.gamma)
+        self.random_ltd_scheduler = None
+        if self.random_ltd_enabled():
+            # random layer-token drop: the scheduler grows the kept-token count; layers wrapped by convert_to_random_ltd
+            # read it (ref: engine.py:365-369)
+            ltd = self.random_ltd_config()
+            ltd["global_batch_size"] = self.train_batch_size()
+            ltd["micro_batch_size"] = self.train_micro_batch_size_per_gpu()
+            self.random_ltd_scheduler = self._configure_random_ltd_scheduler(ltd)
         self.curriculum_scheduler_legacy = None
         if self._config.curriculum_enabled_legacy:
             from .data_pipeline.curriculum_scheduler import CurriculumScheduler
@@ -303,6 +312,7 @@ class DeepSpeedEngine(torch.nn.Module):
                 self.has_moe_layers = True
                 self.num_experts.append(m.num_experts)
                 self._moe_layers.append((name, m))
+                m.deepspeed_moe.wall_clock_breakdown = bool(self._config.wall_clock_breakdown)
                 if dist.is_initialized():
                     m.set_deepspeed_parallelism(self._config.use_data_before_expert_parallel_)
 
@@ -532,6 +542,8 @@ class DeepSpeedEngine(torch.nn.Module):
             self.flops_profiler.start_profile(ignore_list=None)
         if self.progressive_layer_drop is not None and self.module.training:
             kwargs.update(self.progressive_layer_drop.get_state())
+        if self.random_ltd_scheduler is not None and self.module.training:
+            self.random_ltd_scheduler.update_seq(self.global_steps)
         if self.curriculum_scheduler_legacy is not None and self.module.training:
             self.curriculum_scheduler_legacy.update_difficulty(self.global_steps + 1)
             if self._config.curriculum_params_legacy.get("curriculum_type") == "seqlen":
@@ -888,6 +900,9 @@ class DeepSpeedEngine(torch.nn.Module):
 
     def module_state_dict(self, exclude_frozen_parameters: bool = False):
         sd = self.module.state_dict()
+        if self.random_ltd_scheduler is not None:   # checkpoints carry the unwrapped layer names
+            from .data_pipeline.random_ltd import remove_random_ltd_state_dict
+            sd = remove_random_ltd_state_dict(sd)
         if exclude_frozen_parameters:
             frozen = {n for n, p in self.module.named_parameters() if not p.requires_grad}
             sd = {k: v for k, v in sd.items() if k not in frozen}
@@ -976,6 +991,7 @@ class DeepSpeedEngine(torch.nn.Module):
                      frozen_param_shapes=frozen_shapes, frozen_param_fragments=frozen_fragments, shared_params=shared,
                      lr_scheduler=self.lr_scheduler.state_dict() if self.lr_scheduler is not None else None,
                      data_sampler=self.training_data_sampler.state_dict() if getattr(self, "training_data_sampler", None) is not None else None,
+                     random_ltd=self.random_ltd_scheduler.state_dict() if self.random_ltd_scheduler is not None else None,
                      skipped_steps=self.skipped_steps, global_steps=self.global_steps, global_samples=self.global_samples,
                      dp_world_size=self.dp_world_size, mp_world_size=self.mp_world_size,
                      ds_config=self._config._param_dict, ds_version=_version())
@@ -1065,7 +1081,7 @@ class DeepSpeedEngine(torch.nn.Module):
                     raise RuntimeError(f"checkpoint does not match the module: {bad[:8]}")
                 self._load_moe_experts(os.path.join(load_dir, str(tag)), strict=load_module_strict)
             else:
-                self.module.load_state_dict(ckpt["module"], strict=load_module_strict)
+                self.load_module_state_dict(ckpt, strict=load_module_strict)
         else:
             own = dict(self.module.named_buffers())
             for k, v in (ckpt.get("buffers") or {}).items():
@@ -1115,6 +1131,8 @@ class DeepSpeedEngine(torch.nn.Module):
                 self.lr_scheduler.load_state_dict(ckpt["lr_scheduler"])
             if ckpt.get("data_sampler") is not None and getattr(self, "training_data_sampler", None) is not None:
                 self.training_data_sampler.load_state_dict(ckpt["data_sampler"])
+            if ckpt.get("random_ltd") is not None and self.random_ltd_scheduler is not None:
+                self.random_ltd_scheduler.load_state_dict(ckpt["random_ltd"])
         elif self.zero_optimization_stage() == 3:
             # module-only load under ZeRO-3: the trainable weights exist only as fp32 partitions in the optimizer shard
             zpath = self._get_zero_ckpt_name(load_dir, tag)
@@ -1125,7 +1143,7 @@ class DeepSpeedEngine(torch.nn.Module):
         elif hasattr(self.optimizer, "refresh_fp32_params"):
             self.optimizer.refresh_fp32_params()
         reserved = {"module", "buffer_names", "buffers", "optimizer", "param_shapes", "frozen_param_shapes",
-                    "frozen_param_fragments", "shared_params", "lr_scheduler", "skipped_steps", "data_sampler",
+                    "frozen_param_fragments", "shared_params", "lr_scheduler", "skipped_steps", "data_sampler", "random_ltd",
                     "global_steps", "global_samples", "dp_world_size", "mp_world_size", "ds_config", "ds_version"}
         client_state = {k: v for k, v in ckpt.items() if k not in reserved}
         return os.path.join(load_dir, str(tag)), client_state
@@ -1197,7 +1215,9 @@ class DeepSpeedEngine(torch.nn.Module):
             self.checkpoint_engine.save(sd, os.path.join(save_dir, save_filename))
         return True
 
-    save_fp16_model = save_16bit_model
+    def save_fp16_model(self, save_dir, save_filename="pytorch_model.bin"):
+        """Older name of :meth:`save_16bit_model`."""
+        return self.save_16bit_model(save_dir, save_filename)
 
 
 def _version() -> str:

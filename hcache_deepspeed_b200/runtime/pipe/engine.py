@@ -44,6 +44,8 @@ class PipelineEngine(DeepSpeedEngine):
         self.loss_model = self.module.loss_fn
         self.has_bool_tensors = False
         self.total_loss = None
+        self.agg_additional_losses = None
+        self._fwd_additional = {}
         self.agg_loss = torch.tensor(0.0, device=self.device)
         self.pipe_buffers = {"inputs": [], "labels": [], "outputs": [], "grads_in": []}
         self.num_pipe_buffers = 0
@@ -70,6 +72,71 @@ class PipelineEngine(DeepSpeedEngine):
 
     def set_batch_fn(self, fn):
         self.batch_fn = fn
+
+    def set_dataloader(self, loader):
+        """Only the first and the last stage read data (inputs there, labels here)."""
+        if self.is_first_stage() or self.is_last_stage():
+            self.training_dataloader = loader
+            self.data_iterator = iter(loader)
+
+    def set_has_attention_mask(self, value: bool):
+        assert isinstance(value, bool)
+        self.has_attention_mask = value
+
+    def set_train_batch_size(self, train_batch_size):
+        """Change the global batch by changing the number of micro-batches; the micro-batch size stays."""
+        super().set_train_batch_size(train_batch_size)
+        self.micro_batches = self.gradient_accumulation_steps()
+
+    def reset_activation_shape(self):
+        """Forget the tensor shapes exchanged between stages: call when the activation shape is about to change (e.g. a
+        sequence-length curriculum). The next send / receive re-negotiates them (ref: pipe/engine.py:322)."""
+        self._recv_meta = {"act": None, "grad": None}
+        self._sent_meta = {"act": False, "grad": False}
+        for k in self.pipe_buffers:
+            self.pipe_buffers[k] = [None] * self.num_pipe_buffers
+
+    def get_additional_losses(self):
+        """Extra named losses the last stage's loss function returned next to the main one, averaged over the batch."""
+        return getattr(self, "agg_additional_losses", None)
+
+    def log_for_device(self, *msg):
+        """Debug print restricted by ``HDS_PIPE_LOG_STAGE`` / ``HDS_PIPE_LOG_DP`` (-1 = every stage / replica)."""
+        stage = int(os.environ.get("HDS_PIPE_LOG_STAGE", "-1"))
+        dp = int(os.environ.get("HDS_PIPE_LOG_DP", "-1"))
+        if stage in (-1, self.stage_id) and dp in (-1, self.grid.data_parallel_id):
+            print(f"RANK={self.global_rank} PIPE-ID={self.stage_id} DATA-ID={self.grid.data_parallel_id} "
+                  f"STEP-ID={self.global_steps} ::", *msg, flush=True)
+
+    def tput_log(self, *msg):
+        if self.global_rank == 0 and self.global_steps % max(1, self.steps_per_print() or 1) == 0:
+            print(*msg)
+
+    def mem_status(self, msg, print_rank=-1, reset_max=False):
+        """Allocator numbers of this rank, printed on ``print_rank`` (or everywhere for -1); returns them."""
+        if not torch.cuda.is_available():
+            return None
+        if reset_max:
+            torch.cuda.reset_peak_memory_stats()
+        gb = 1024 ** 3
+        stats = {"allocated_gb": torch.cuda.memory_allocated() / gb, "max_allocated_gb": torch.cuda.max_memory_allocated() / gb,
+                 "reserved_gb": torch.cuda.memory_reserved() / gb, "max_reserved_gb": torch.cuda.max_memory_reserved() / gb}
+        if print_rank in (-1, self.global_rank):
+            print(f"RANK={self.global_rank} STAGE={self.stage_id} STEP={self.global_steps} MEMSTATS {msg} "
+                  + " ".join(f"{k}={v:.4f}" for k, v in stats.items()), flush=True)
+        return stats
+
+    def load_module_state_dict(self, checkpoint, strict=True, custom_load_fn=None, fetch_z3_params=False):
+        """Pipeline weights live one file per layer: a checkpoint whose ``module`` entry is empty (or a directory path)
+        is loaded with ``PipelineModule.load_state_dir``; a plain state dict falls through to the base engine."""
+        assert custom_load_fn is None, "custom_load_fn not supported w. pipeline parallelism"
+        sd = checkpoint.get("module") if isinstance(checkpoint, dict) else checkpoint
+        if sd is not None and not isinstance(sd, str):
+            return super().load_module_state_dict(checkpoint, strict=strict)
+        load_dir = sd if isinstance(sd, str) else getattr(self, "_curr_ckpt_path", None)
+        if load_dir is None:
+            raise ValueError("no per-layer checkpoint directory: pass its path as checkpoint['module']")
+        self.module.load_state_dir(load_dir, self.checkpoint_engine, strict=strict)
 
     def set_has_bool_tensors(self, v: bool):
         self.has_bool_tensors = v
@@ -98,6 +165,7 @@ class PipelineEngine(DeepSpeedEngine):
         self.module.train()
         self.total_loss = None
         self._fwd_losses = []
+        self._fwd_additional = {}
         sched = schedule.TrainSchedule(micro_batches=self.micro_batches, stages=self.num_stages, stage_id=self.stage_id)
         self._exec_schedule(sched)
         self.agg_train_loss = self._aggregate_total_loss()
@@ -152,7 +220,31 @@ class PipelineEngine(DeepSpeedEngine):
                 loss /= self.grid.data_parallel_size
         else:
             loss = torch.tensor(0.0, device=self.device)
+        self._aggregate_additional_losses()
         return self._bcast_pipe_scalar(loss)
+
+    def _aggregate_additional_losses(self):
+        """Mean over micro-batches and data-parallel replicas of every named side loss, then last stage -> all stages.
+        As in the reference, ``module.get_additional_losses()`` must name the same losses on every stage."""
+        from collections import OrderedDict
+        if self.is_last_stage():
+            names = list(self._fwd_additional)
+        else:
+            extra = self.module.get_additional_losses()
+            names = list(extra) if extra is not None else []
+        if not names:
+            self.agg_additional_losses = None
+            return
+        if self.is_last_stage():
+            vals = torch.stack([torch.stack(self._fwd_additional[n]).mean() for n in names]).to(self.device)
+            if self.grid is not None and self.grid.data_parallel_size > 1:
+                dist.all_reduce(vals, group=self.grid.get_data_parallel_group())
+                vals /= self.grid.data_parallel_size
+        else:
+            vals = torch.zeros(len(names), device=self.device)
+        if self.num_stages > 1:
+            dist.broadcast(vals, src=self.grid.stage_to_global(self.num_stages - 1), group=self.grid.get_pipe_parallel_group())
+        self.agg_additional_losses = OrderedDict((n, vals[i].clone()) for i, n in enumerate(names))
 
     # ------------------------------------------------------------------------------------------------
     # instruction handlers
@@ -189,6 +281,10 @@ class PipelineEngine(DeepSpeedEngine):
                 loss = self.loss_model(outputs, self.pipe_buffers["labels"][buffer_id])
                 self.pipe_buffers["outputs"][buffer_id] = loss
                 self._fwd_losses.append(loss.detach())
+                extra = self.module.get_additional_losses()
+                if extra is not None:   # named side losses of this micro-batch (ref: pipe/engine.py:796-802)
+                    for name, v in extra.items():
+                        self._fwd_additional.setdefault(name, []).append(v.detach().float())
             else:
                 if hasattr(self, "_eval_outputs"):
                     self._eval_outputs.append(outputs.detach() if torch.is_tensor(outputs) else outputs)

@@ -277,6 +277,31 @@ class PipelineModule(nn.Module):
         mp = self._grid.get_slice_parallel_rank() if self._grid is not None else 0
         return os.path.join(ckpt_dir, f"layer_{global_idx:02d}-model_{mp:02d}-model_states.pt")
 
+    def ckpt_layer_path_list(self, ckpt_dir: str, local_layer_idx: int) -> List[str]:
+        """Every model-parallel slice file of this stage's ``local_layer_idx``-th layer, sorted."""
+        import glob
+        idx = local_layer_idx + self._local_start
+        return sorted(glob.glob(os.path.join(ckpt_dir, f"layer_{idx:02d}-*model_states.pt")))
+
+    def set_checkpoint_interval(self, interval: int) -> None:
+        """Layers per activation-checkpointed segment (0 = no activation checkpointing)."""
+        assert interval >= 0
+        self.activation_checkpoint_interval = interval
+
+    @property
+    def checkpoint_interval(self) -> int:
+        return self.activation_checkpoint_interval
+
+    def get_additional_losses(self):
+        """Override to report named side losses (``{"name": tensor}``) next to the main loss; ``None`` = none."""
+        return None
+
+    def compile(self, *args, **kwargs) -> None:
+        """The reference wraps each layer in ``torch.compile`` here (pipe/module.py:687). This framework has no tracing
+        compiler in its hot path: the stage's layers run as written (their fused CUDA ops are already single launches)
+        and the call is accepted so scripts that issue it keep working."""
+        self._compile_requested = (args, kwargs)
+
     def save_state_dict(self, save_dir: str, checkpoint_engine, exclude_frozen_params: bool = False) -> None:
         dp_rank = self._grid.data_parallel_id if self._grid is not None else 0
         if dp_rank != 0:

@@ -56,3 +56,73 @@ def get_state_devices(model, state: OffloadStateTypeEnum) -> Set[torch.device]:
     if state == OffloadStateTypeEnum.lp_grads:
         return {p.grad.device for p in model.module.parameters() if p.grad is not None} if hasattr(model, "module") else set()
     return set()
+
+
+# ---- whole-engine state movement (engine.offload_states / reload_states) -------------------------------------------------
+def _engine_state_tensors(engine, kind: OffloadStateTypeEnum):
+    """The tensors that make up one kind of state of ``engine``, whichever ZeRO stage (or none) it runs."""
+    from .partition_parameters import is_zero_param
+    opt = engine.optimizer
+    base = getattr(opt, "optimizer", opt)
+    if kind == OffloadStateTypeEnum.optim_states:
+        return [t for st in getattr(base, "state", {}).values() for k, t in st.items()
+                if torch.is_tensor(t) and t.dim() > 0 and not k.endswith("_offload_buffer")]
+    if kind == OffloadStateTypeEnum.hp_params:
+        return [t for t in (getattr(opt, "fp32_partitioned_groups_flat", None) or getattr(opt, "single_partition_of_fp32_groups", None)
+                            or []) if t.numel()]
+    if kind == OffloadStateTypeEnum.lp_params:
+        out = []
+        for p in engine.module.parameters():
+            if is_zero_param(p):
+                if getattr(p, "ds_tensor", None) is not None and not getattr(p, "ds_nvme", False):
+                    out.append(p.ds_tensor)
+            else:
+                out.append(p)
+        return out
+    if kind == OffloadStateTypeEnum.lp_grads:
+        parts = getattr(opt, "grad_partitions", None)
+        if isinstance(parts, dict) and parts:
+            return [g for g in parts.values() if torch.is_tensor(g)]
+        return [p.grad for p in engine.module.parameters() if p.grad is not None]
+    if kind == OffloadStateTypeEnum.contiguous_grad_buffer:
+        buf = getattr(opt, "ipg_buffer", None) or getattr(opt, "_grad_flat", None)
+        return [b for b in (buf if isinstance(buf, (list, tuple)) else [buf]) if torch.is_tensor(b)]
+    return []
+
+
+def offload_engine_states(engine, include=None, device=torch.device("cpu"), pin_memory: bool = True, non_blocking: bool = False) -> None:
+    """Move the chosen kinds of state to ``device``, remembering where each tensor lived. Host buffers are kept across
+    calls (pinned when asked and possible) so repeated offload / reload cycles - one per RLHF phase - do not re-allocate."""
+    kinds = [OffloadStateTypeEnum(k) for k in include] if include is not None else list(OffloadStateTypeEnum)
+    record = engine.__dict__.setdefault("_offloaded_states", {})      # id(tensor) -> (tensor, home device, kind)
+    buffers = engine.__dict__.setdefault("_offload_host_buffers", {})  # id(tensor) -> host buffer
+    can_pin = pin_memory and torch.cuda.is_available() and device.type == "cpu"
+    for kind in kinds:
+        for t in _engine_state_tensors(engine, kind):
+            if id(t) in record:
+                continue
+            buf = buffers.get(id(t))
+            if buf is None or buf.shape != t.shape or buf.dtype != t.dtype:
+                buf = torch.empty(t.shape, dtype=t.dtype, device=device)
+                if can_pin:
+                    buf = buf.pin_memory()
+                buffers[id(t)] = buf
+            buf.copy_(t.data, non_blocking=non_blocking)
+            record[id(t)] = (t, t.device, kind)
+            t.data = buf
+    if torch.cuda.is_available() and not non_blocking:
+        torch.cuda.synchronize()
+        torch.cuda.empty_cache()
+
+
+def reload_engine_states(engine, non_blocking: bool = False) -> None:
+    record = engine.__dict__.get("_offloaded_states") or {}
+    for t, home, _ in record.values():
+        t.data = t.data.to(home, non_blocking=non_blocking) if t.data.device != home else t.data.clone()
+    record.clear()
+    if torch.cuda.is_available() and not non_blocking:
+        torch.cuda.synchronize()
+
+
+def offloaded_state_kinds(engine) -> Set[OffloadStateTypeEnum]:
+    return {kind for _, _, kind in (engine.__dict__.get("_offloaded_states") or {}).values()}

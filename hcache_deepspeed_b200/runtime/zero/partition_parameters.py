@@ -264,6 +264,21 @@ class Init:
         if module is not None and enabled:
             self._convert_module(module)
 
+    # ---- partitioning geometry (ref: partition_parameters.py:2103-2117) ----------------------------------------------------
+    def get_partition_dp_group(self, param):
+        return param.ds_process_group
+
+    def get_dp_process_group(self):
+        """The group parameters are partitioned over (``None`` = the default world group)."""
+        return self.group
+
+    def get_partition_rank(self) -> int:
+        return _group_info(self.group)[1]
+
+    @property
+    def num_partitions(self) -> int:
+        return _group_info(self.group)[0]
+
     def _convert_module(self, module: torch.nn.Module):
         for p in module.parameters(recurse=True):
             _convert(p, self.group, self.remote_device, self.pin_memory, self.persistence_threshold, self.dtype)

@@ -694,3 +694,130 @@ def safe_accessors_worker(rank, world, stage):
     else:
         out["lp_follows"] = float((p.data.float() - 0.25).abs().max())
     return out
+
+
+def engine_accessors_worker(rank, world, stage):
+    """Public helpers of the engine that other frameworks call directly: bucketed all-reduce, sparse all-reduce, scalar
+    all-gather, state offload / reload, partition-cache release, module-state loading (ref: engine.py:2560-2720, 3943)."""
+    import hcache_deepspeed_b200 as ds
+    from hcache_deepspeed_b200.runtime.sparse_tensor import SparseTensor
+    from hcache_deepspeed_b200.runtime.zero.offload_states import OffloadStateTypeEnum, offloaded_state_kinds
+    ds.init_distributed(dist_backend="gloo")
+    torch.manual_seed(0)
+    model = TinyNet(32)
+    cfg = {"train_micro_batch_size_per_gpu": 4, "optimizer": {"type": "Adam", "params": {"lr": 1e-2}}, "steps_per_print": 1000,
+           "zero_optimization": {"stage": stage, "stage3_param_persistence_threshold": 0}}
+    engine, _, _, _ = ds.initialize(model=model, config=cfg)
+    group = engine.data_parallel_group
+    out = {}
+    # bucket helpers
+    a, b = torch.full((3, ), float(rank + 1)), torch.full((2, 2), float(10 * (rank + 1)))
+    engine.allreduce_no_retain([a, b], group, numel_per_bucket=3)
+    mean = sum(range(1, world + 1)) / world
+    out["bucket"] = (float(a[0]), float(b[0, 0]), mean)
+    out["scalars"] = [int(t) for t in engine.all_gather_scalar(torch.tensor([rank + 5]), group)]
+    dense = torch.zeros(6, 2)
+    dense[rank] = 1.0 + rank
+    st = engine.sparse_allreduce(SparseTensor(dense), group)
+    out["sparse_rows"] = sorted(st.indices.tolist())
+    out["sparse_dense"] = st.to_dense()[:world, 0].tolist()
+    # one training step, then offload everything, reload, and train on: same result as without the round trip
+    x, y = next(iter(make_batches(1, 4 * world, 32)))
+    lo = rank * 4
+
+    def step(e):
+        loss = e(x[lo:lo + 4], y[lo:lo + 4])
+        e.backward(loss)
+        e.step()
+        return float(loss)
+
+    step(engine)
+    engine.offload_states(pin_memory=False)
+    out["kinds"] = sorted(k.value for k in offloaded_state_kinds(engine))
+    engine.reload_states()
+    out["kinds_after"] = len(offloaded_state_kinds(engine))
+    engine.offload_states(include=[OffloadStateTypeEnum.optim_states, OffloadStateTypeEnum.hp_params], pin_memory=False)
+    engine.reload_states()
+    l_round_trip = step(engine)
+    torch.manual_seed(0)
+    model2 = TinyNet(32)
+    engine2, _, _, _ = ds.initialize(model=model2, config=cfg)
+    step(engine2)
+    out["loss_pair"] = (l_round_trip, step(engine2))
+    # partition cache + module state loading
+    if stage == 3:
+        from hcache_deepspeed_b200.runtime.zero import GatheredParameters, ZeroParamStatus
+        from hcache_deepspeed_b200.runtime.zero.partition_parameters import all_gather_params
+        ps = list(engine.module.parameters())
+        all_gather_params(ps)
+        engine.empty_partition_cache()
+        out["released"] = all(p.ds_status == ZeroParamStatus.NOT_AVAILABLE for p in ps)
+        sd = {k: torch.full_like(v, 0.5) for k, v in TinyNet(32).state_dict().items()}
+        engine.load_module_state_dict({"module": sd}, fetch_z3_params=True)
+        with GatheredParameters(ps):
+            out["loaded"] = all(float((p.data - 0.5).abs().max()) == 0.0 for p in ps)
+    else:
+        sd = {k: torch.full_like(v, 0.5) for k, v in engine.module.state_dict().items()}
+        engine.load_module_state_dict({"module": sd})
+        out["loaded"] = all(float((p.data.float() - 0.5).abs().max()) == 0.0 for p in engine.module.parameters())
+        out["released"] = True
+    return out
+
+
+def pipe_api_worker(rank, world):
+    """Smaller public methods of the pipeline engine / module: named side losses, changing the batch size and the
+    activation shape between batches, per-layer file listing, loading layer files through ``load_module_state_dict``."""
+    import tempfile
+    import hcache_deepspeed_b200 as ds
+    from hcache_deepspeed_b200.runtime.pipe import LayerSpec, PipelineModule
+    ds.init_distributed(dist_backend="gloo")
+    hidden, micro = 16, 4
+
+    class Net(PipelineModule):
+        aux = None
+
+        def get_additional_losses(self):
+            return {"l1": Net.aux if Net.aux is not None else torch.zeros(())}
+
+    def loss_fn(out, y):
+        Net.aux = out.detach().abs().mean()
+        return torch.nn.functional.mse_loss(out.squeeze(-1), y)
+
+    torch.manual_seed(7)
+    specs = [LayerSpec(_Stage, hidden) for _ in range(3)] + [LayerSpec(torch.nn.Linear, hidden, 1)]
+    net = Net(layers=specs, num_stages=2, loss_fn=loss_fn, partition_method="uniform", seed_layers=True, base_seed=100)
+    cfg = {"train_micro_batch_size_per_gpu": micro, "gradient_accumulation_steps": 2,
+           "optimizer": {"type": "Adam", "params": {"lr": 1e-2, "torch_adam": True}}, "steps_per_print": 1000}
+    engine, _, _, _ = ds.initialize(model=net, config=cfg)
+    out = {"stage": engine.stage_id}
+
+    def batches(n, rows=micro, seed=0):
+        g = torch.Generator().manual_seed(seed)
+        return iter([(torch.randn(rows, hidden, generator=g), torch.randn(rows, generator=g)) for _ in range(n)])
+
+    engine.train_batch(batches(2))
+    extra = engine.get_additional_losses()
+    out["extra"] = {k: float(v) for k, v in extra.items()}
+    engine.set_train_batch_size(micro * 3)                     # 3 micro-batches now
+    out["micro_batches"] = (engine.micro_batches, engine.gradient_accumulation_steps())
+    engine.train_batch(batches(3, seed=1))
+    engine.reset_activation_shape()                            # other row count per micro-batch from here on
+    out["loss_new_shape"] = float(engine.train_batch(batches(3, rows=2, seed=2)))
+    net.set_checkpoint_interval(1)
+    out["interval"] = net.checkpoint_interval
+    out["loss_ckpt"] = float(engine.train_batch(batches(3, rows=2, seed=3)))
+    # per-layer files
+    d = os.environ.get("HDS_TEST_PIPE_DIR")
+    engine.save_checkpoint(d, tag="t")
+    ds.comm.barrier()
+    out["files"] = [os.path.basename(p) for p in net.ckpt_layer_path_list(os.path.join(d, "t"), 0)]
+    before = [p.detach().clone() for p in net.parameters()]
+    with torch.no_grad():
+        for p in net.parameters():
+            p.zero_()
+    engine.load_module_state_dict({"module": os.path.join(d, "t")})
+    out["reloaded"] = all(torch.equal(a, b) for a, b in zip(before, net.parameters()))
+    engine.tput_log("pipeline api worker done")
+    engine.log_for_device("stage", engine.stage_id)
+    out["mem"] = engine.mem_status("end")
+    return out

@@ -245,3 +245,63 @@ def test_engine_builds_curriculum_sampler_from_data_efficiency_config(tmp_path):
     engine2.load_checkpoint(str(tmp_path), tag="c")
     st = engine2.training_data_sampler.state_dict()
     assert st["consumed_samples"] == saved["consumed_samples"] > 0 and st["curriculum_step"] == saved["curriculum_step"]
+
+
+def test_engine_runs_random_ltd_schedule_and_checkpoints_it(tmp_path):
+    """``data_efficiency.data_routing.random_ltd`` on the engine: the scheduler is created by the engine, handed to the
+    wrapped layers by ``convert_to_random_ltd`` -> ``engine.random_ltd_initialize()``, advanced every forward, saved and
+    restored with the checkpoint, and checkpoints carry the unwrapped key names (ref: engine.py:365-369, 691, 2002, 2766)."""
+    import hcache_deepspeed_b200 as ds
+    from hcache_deepspeed_b200.runtime.data_pipeline.data_routing import RandomLayerTokenDrop, convert_to_random_ltd
+
+    class Block(torch.nn.Module):
+        def __init__(self):
+            super().__init__()
+            self.fc = torch.nn.Linear(8, 8)
+            self.seen = []
+
+        def forward(self, x):
+            self.seen.append(x.shape[1])
+            return x + torch.tanh(self.fc(x))
+
+    class Net(torch.nn.Module):
+        def __init__(self):
+            super().__init__()
+            self.blocks = torch.nn.ModuleList([Block() for _ in range(3)])
+
+        def forward(self, x):
+            for b in self.blocks:
+                x = b(x)
+            return x.pow(2).mean()
+
+    def build():
+        torch.manual_seed(0)
+        cfg = {"train_micro_batch_size_per_gpu": 2, "optimizer": {"type": "SGD", "params": {"lr": 0.01}}, "steps_per_print": 1000,
+               "data_efficiency": {"enabled": True, "data_routing": {"enabled": True, "random_ltd": {
+                   "enabled": True, "total_layer_num": 3, "random_ltd_layer_num": 2, "random_ltd_layer_id": [1, 2],
+                   "random_ltd_schedule": {"min_value": 4, "max_value": 16, "schedule_type": "fixed_linear",
+                                           "schedule_config": {"require_steps": 4, "seq_per_step": 4}}}}}}
+        engine, _, _, _ = ds.initialize(model=Net(), config=cfg)
+        convert_to_random_ltd(engine, Block)
+        return engine
+
+    engine = build()
+    assert engine.random_ltd_enabled() and engine.random_ltd_scheduler is not None
+    wrapped = [m for m in engine.module.modules() if isinstance(m, RandomLayerTokenDrop)]
+    assert len(wrapped) == 3 and [w.scheduler is engine.random_ltd_scheduler for w in wrapped] == [False, True, True]
+    x = torch.randn(2, 16, 8)
+    kept = []
+    for _ in range(5):
+        loss = engine(x)
+        engine.backward(loss)
+        engine.step()
+        kept.append(engine.module.blocks[1].random_ltd_layer.seen[-1])
+        assert engine.module.blocks[0].random_ltd_layer.seen[-1] == 16      # not in random_ltd_layer_id: every token
+    assert kept == [4, 4, 8, 12, 16], kept
+    assert not any("random_ltd_layer" in k for k in engine.module_state_dict())
+    engine.save_checkpoint(str(tmp_path), tag="t")
+    fresh = build()
+    fresh.load_checkpoint(str(tmp_path), tag="t")
+    assert fresh.random_ltd_scheduler.state_dict() == engine.random_ltd_scheduler.state_dict()
+    for a, b in zip(fresh.module.parameters(), engine.module.parameters()):
+        assert torch.equal(a, b)

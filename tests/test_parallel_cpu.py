@@ -149,3 +149,29 @@ def test_ulysses_training_through_the_engine_matches_full_sequence():
     from tests.parallel_helper import ulysses_engine_worker
     for r in run_distributed(ulysses_engine_worker, 2):
         assert r["sp"] == 2 and r["got"] == pytest.approx(r["want"], rel=1e-5, abs=1e-5), r
+
+
+def test_moe_wall_clock_breakdown_counters_and_engine_report():
+    """``wall_clock_breakdown`` switches on the MoE layer's gate / all-to-all / total timers, and
+    ``engine.print_forward_breakdown`` sums them over the model's MoE layers (ref: sharded_moe.py:590-650, engine.py:2050)."""
+    import hcache_deepspeed_b200 as ds
+    from hcache_deepspeed_b200.moe.layer import MoE
+
+    class Net(torch.nn.Module):
+        def __init__(self):
+            super().__init__()
+            self.a = MoE(8, torch.nn.Linear(8, 8), num_experts=2, ep_size=1, min_capacity=4)
+            self.b = MoE(8, torch.nn.Linear(8, 8), num_experts=2, ep_size=1, min_capacity=4)
+
+        def forward(self, x):
+            return self.b(self.a(x)[0])[0].pow(2).mean()
+
+    engine, _, _, _ = ds.initialize(model=Net(), config={"train_micro_batch_size_per_gpu": 2, "wall_clock_breakdown": True,
+                                                         "optimizer": {"type": "SGD", "params": {"lr": 0.1}}, "steps_per_print": 1000})
+    layers = [engine.module.a.deepspeed_moe, engine.module.b.deepspeed_moe]
+    assert all(l.wall_clock_breakdown for l in layers) and all(l.time_moe == 0.0 for l in layers)
+    engine(torch.randn(2, 4, 8))
+    assert all(l.time_moe > 0.0 and 0.0 < l.gate_time <= l.time_moe for l in layers)
+    rep = engine.print_forward_breakdown(fwd_time=12.5)
+    assert rep["fwd"] == 12.5 and rep["fwd_moe"] == pytest.approx(sum(l.time_moe for l in layers))
+    assert rep["top_k"] == pytest.approx(sum(l.gate_time for l in layers)) and rep["1st_a2a"] >= 0.0

@@ -212,3 +212,45 @@ def test_continuous_batching_with_chunked_prefill_matches_sequential_oracle():
     bad = [u for u in range(N) if done[u] != oracle[u]]
     assert not bad, bad
     assert int(eng.free_blocks.min()) == total_blocks and steps < 60
+
+
+def test_reference_accessor_surface_of_wrapper_cache_and_manager():
+    """Accessors of the reference's ragged classes (ragged_wrapper.py:230-276, kv_cache.py:144-201, ragged_manager.py:170)."""
+    import torch
+    from hcache_deepspeed_b200.inference.v2 import RaggedInferenceEngineConfig, build_engine_from_arch
+    from hcache_deepspeed_b200.models.arch import named_arch
+    cfg = RaggedInferenceEngineConfig(state_manager=dict(max_tracked_sequences=4, max_ragged_batch_size=64, max_ragged_sequence_count=2,
+                                                         max_context=512, memory_config=dict(mode="allocate", size=8 << 20)))
+    eng = build_engine_from_arch(named_arch("tiny-llama-test"), cfg, dtype=torch.float32, device=torch.device("cpu"))
+    eng.put([1, 2], [torch.arange(5), torch.arange(3)])
+    b = eng._batch
+    assert b.inflight_seq_descriptors().tolist() == [[0, 5, 0, 0], [5, 3, 0, 0]]
+    assert b.batch_metadata_buffer().tolist() == [8, 2]
+    assert b.kv_ptrs().shape[0] == 2 and b.masks() is None
+    sm = eng._state_manager
+    kv = sm.kv_cache
+    before = kv.free_blocks[0]
+    ids = kv.reserve(2)
+    assert kv.free_blocks[0] == before - 2 and int(sm.free_blocks[0]) == before - 2
+    kv.free(ids)
+    assert kv.free_blocks[0] == before
+    assert sm.get_sequence(1).max_context >= 1
+
+    # restore_kv with a caller-supplied projection fills the sequence's pages, spanning several blocks
+    bs = sm.kv_block_size
+    layers, heads, hd = kv.num_caches, kv.get_cache(0).shape[2], kv.get_cache(0).shape[4]
+    n_tok, hidden = bs + 3, 16
+    g = torch.Generator().manual_seed(0)
+    latent = [torch.randn(n_tok, hidden, generator=g) for _ in range(layers)]
+    w = [torch.randn(hidden, 2 * heads * hd, generator=g) for _ in range(layers)]
+    got = sm.restore_kv(9, latent, lambda x, wl, b=None: x @ wl, w)
+    seq = sm.get_sequence(9)
+    assert got == n_tok and seq.seen_tokens == n_tok and seq.cur_allocated_blocks == 2
+    blocks = seq.all_block_ids.tolist()
+    for l in range(layers):
+        want = (latent[l] @ w[l]).reshape(n_tok, 2, heads, hd)
+        cache = kv.get_cache(l)
+        for t in (0, bs - 1, bs, n_tok - 1):
+            torch.testing.assert_close(cache[blocks[t // bs], :, :, t % bs], want[t])
+    sm.flush_sequence(9)
+    assert kv.free_blocks[0] == before

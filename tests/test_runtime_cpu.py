@@ -625,3 +625,62 @@ def test_unwrap_model_for_generation_gathers_once():
     engine.backward(loss)
     engine.step()
     assert float((engine(x).detach() - want).abs().max()) > 0
+
+
+def test_engine_config_getters_follow_the_config():
+    """The reference's one-line engine getters (engine.py:480-960), generated here from one table."""
+    import hcache_deepspeed_b200 as ds
+    cfg = {"train_micro_batch_size_per_gpu": 2, "optimizer": {"type": "Adam", "params": {"lr": 1e-3}}, "steps_per_print": 1000,
+           "zero_optimization": {"stage": 2, "reduce_bucket_size": 1234, "allgather_bucket_size": 4321, "overlap_comm": True,
+                                 "contiguous_gradients": False, "round_robin_gradients": True},
+           "flops_profiler": {"enabled": False, "profile_step": 7, "top_modules": 3, "module_depth": 2},
+           "eigenvalue": {"enabled": False, "max_iter": 11, "tol": 0.5},
+           "data_efficiency": {"enabled": True, "data_sampling": {"enabled": False},
+                               "data_routing": {"enabled": True, "random_ltd": {"enabled": False}}},
+           "compression_training": {"weight_quantization": {"shared_parameters": {"enabled": True, "quantize_groups": 4,
+                                                                                   "quantization_type": "asymmetric"}}}}
+    engine, _, _, _ = ds.initialize(model=torch.nn.Linear(4, 4), config=cfg)
+    assert engine.zero_reduce_bucket_size() == 1234 and engine.zero_allgather_bucket_size() == 4321
+    assert engine.zero_overlap_comm() is True and engine.zero_contiguous_gradients() is False and engine.zero_round_robin_gradients()
+    assert engine.zero_optimization_partition_gradients() and not engine.zero_optimization_partition_weights()
+    assert not engine.zero_use_cpu_optimizer() and engine.zero_partial_offload() == 1.0 and engine.mics_shard_size() == -1
+    assert engine.flops_profiler_profile_step() == 7 and engine.flops_profiler_top_modules() == 3 and engine.flops_profiler_module_depth() == 2
+    assert not engine.flops_profiler_enabled() and not engine.autotuning_enabled()
+    assert engine.eigenvalue_max_iter() == 11 and engine.eigenvalue_tol() == 0.5 and not engine.eigenvalue_enabled()
+    assert engine.data_efficiency_enabled() and not engine.data_sampling_enabled() and not engine.random_ltd_enabled()
+    assert not engine.curriculum_learning_enabled() and engine.get_pld_theta() is None
+    q = engine.quantize_training()
+    assert q[1] is True and q[2] == 4 and q[5] == "asymmetric"
+    assert engine.is_map_style_dataset([1, 2]) and not engine.is_iterable_style_dataset([1, 2])
+    assert engine.autotuning_metric_path().endswith("autotuning_metric.json")
+    assert engine.get_sequence_parallel_group() is engine.seq_parallel_group
+    # every getter of the table is callable and none raises on a minimal config
+    from hcache_deepspeed_b200.runtime.engine_accessors import _CONFIG_GETTERS
+    bare, _, _, _ = ds.initialize(model=torch.nn.Linear(4, 4), config={"train_batch_size": 1})
+    for name in _CONFIG_GETTERS:
+        getattr(bare, name)()
+
+
+@pytest.mark.parametrize("stage", [0, 2, 3])
+def test_engine_public_helpers_2ranks(stage):
+    from tests.runtime_helper import engine_accessors_worker
+    for r in run_distributed(engine_accessors_worker, 2, stage):
+        a, b, mean = r["bucket"]
+        assert a == mean and b == 10 * mean, r
+        assert r["scalars"] == [5, 6] and r["sparse_rows"] == [0, 1], r
+        assert r["sparse_dense"] == [0.5, 1.0], r
+        assert "optim_states" in r["kinds"] and "lp_params" in r["kinds"] and r["kinds_after"] == 0, r
+        assert abs(r["loss_pair"][0] - r["loss_pair"][1]) < 1e-7, r
+        assert r["released"] and r["loaded"], r
+
+
+def test_pipeline_engine_small_public_methods_2stages(tmp_path, monkeypatch):
+    from tests.runtime_helper import pipe_api_worker
+    monkeypatch.setenv("HDS_TEST_PIPE_DIR", str(tmp_path))
+    res = run_distributed(pipe_api_worker, 2)
+    assert res[0]["extra"].keys() == {"l1"} and res[0]["extra"] == res[1]["extra"] and res[0]["extra"]["l1"] > 0
+    for r in res:
+        assert r["micro_batches"] == (3, 3) and r["interval"] == 1 and r["reloaded"], r
+        assert r["loss_new_shape"] == res[0]["loss_new_shape"] and r["loss_ckpt"] == res[0]["loss_ckpt"]
+        assert r["mem"] is None
+    assert res[0]["files"] == ["layer_00-model_00-model_states.pt"] and res[1]["files"] == ["layer_02-model_00-model_states.pt"]

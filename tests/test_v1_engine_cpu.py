@@ -269,3 +269,65 @@ def test_int8_dtype_selects_8bit_serving():
     got = eng(ids).logits
     assert isinstance(eng.ragged_engine.model().w.layers[0].w_qkv, Fp8Weight)
     assert torch.nn.functional.cosine_similarity(got.flatten(), want.flatten(), dim=0) > 0.99
+
+
+def test_v1_engine_model_fixups_and_compile_flag():
+    """``build_alibi_tensor`` / ``build_attn_bias`` / ``remove_mask_prepare_for_bloom`` / ``compile`` of the v1 engine
+    (ref: inference/engine.py:207-228, 608-625), on stand-in modules with the attribute layout of BLOOM, MPT and Baichuan."""
+    import types
+    import hcache_deepspeed_b200 as ds
+    from hcache_deepspeed_b200.module_inject.auto_tp_model_utils import build_bloom_alibi_tensor, slice_heads
+
+    class Inner(torch.nn.Module):
+        def __init__(self):
+            super().__init__()
+            self.fc = torch.nn.Linear(4, 4)
+
+        def build_alibi_tensor(self, attention_mask, num_heads, dtype):
+            raise AssertionError("replaced by the engine")
+
+        def build_mpt_alibi_tensor(self, heads, seq):
+            return torch.arange(heads * seq, dtype=torch.float32).reshape(1, heads, 1, seq)
+
+        def _attn_bias(self, device, dtype, attention_mask=None, prefix_mask=None, sequence_id=None):
+            return torch.arange(8 * 3, dtype=dtype).reshape(1, 8, 1, 3), attention_mask
+
+        def _prepare_attn_mask(self, attention_mask, *a, **k):
+            return attention_mask * 0
+
+        def get_alibi_mask(self, tensor, seq):
+            return torch.arange(8 * seq * seq, dtype=torch.float32).reshape(8, seq, seq)
+
+    class Model(torch.nn.Module):
+        def __init__(self):
+            super().__init__()
+            self.transformer = Inner()
+            self.model = self.transformer
+
+        def forward(self, x):
+            return self.transformer.fc(x)
+
+    eng = ds.init_inference(Model(), dtype=torch.float32)
+    eng.build_alibi_tensor()
+    eng.build_attn_bias()
+    eng.remove_mask_prepare_for_bloom()
+    tr = eng.module.transformer
+    mask = torch.ones(2, 5, dtype=torch.long)
+    torch.testing.assert_close(tr.build_alibi_tensor(mask, 8, torch.float32), build_bloom_alibi_tensor(mask, 8, torch.float32, 1, 0))
+    assert tr.build_mpt_alibi_tensor(8, 3).shape == (1, 8, 1, 3)              # tp = 1: all heads
+    bias, m = tr._attn_bias("cpu", torch.float32, attention_mask=mask)
+    assert bias.shape == (1, 8, 1, 3) and m is mask
+    assert torch.equal(tr._prepare_attn_mask(mask), mask)
+    assert tr.get_alibi_mask(None, 4).shape == (8, 4, 4)
+    # the slicing helper the patched builders use under tp > 1: uneven head counts follow the attention sharding
+    t = torch.arange(7 * 2).reshape(1, 7, 2)
+    parts = [slice_heads(t, 1, r, 3) for r in range(3)]
+    assert [p.shape[1] for p in parts] == [3, 2, 2] and torch.equal(torch.cat(parts, 1), t)
+    assert eng.is_compiled is False
+    eng.compile()
+    assert eng.is_compiled is True and eng._config.enable_cuda_graph is True
+    x = torch.randn(2, 4)
+    torch.testing.assert_close(eng(x), eng.module(x))                           # CPU: graph flag is inert
+    import pytest
+    with pytest.raises(ValueError):
+        eng.load_model_with_checkpoint()
