@@ -1125,7 +1125,8 @@ class DeepSpeedEngine(EngineAccessors, torch.nn.Module):
                     if os.path.exists(own_path):
                         osd = self.checkpoint_engine.load(own_path, map_location="cpu")["optimizer"]
                 self.optimizer.load_state_dict(osd)
-            if zero_wrapped and not load_optimizer_states and hasattr(self.optimizer, "refresh_fp32_params"):
+            if zero_wrapped and not load_optimizer_states and self.zero_optimization_stage() != 3 and \
+                    hasattr(self.optimizer, "refresh_fp32_params"):   # (stage 3 restored its fp32 masters from the shard file)
                 self.optimizer.refresh_fp32_params()
             if load_lr_scheduler_states and self.lr_scheduler is not None and ckpt.get("lr_scheduler") is not None:
                 self.lr_scheduler.load_state_dict(ckpt["lr_scheduler"])

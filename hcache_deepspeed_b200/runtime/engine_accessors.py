@@ -359,10 +359,13 @@ class EngineAccessors:
             params = [p for p in self.module.parameters() if is_zero_param(p)]
             with GatheredParameters(params, modifier_rank=0):
                 load()
-            if hasattr(self.optimizer, "refresh_fp32_params"):
-                self.optimizer.refresh_fp32_params()
         else:
             load()
+        if self.zero_optimization_stage() != 3 or fetch_z3_params:
+            # the fp32 master copy follows the weights just loaded (a full checkpoint load restores it from the
+            # optimizer shard afterwards anyway)
+            if hasattr(self.optimizer, "refresh_fp32_params"):
+                self.optimizer.refresh_fp32_params()
 
     @staticmethod
     def load_moe_state_dict(checkpoint_path, tag, state_dict, old_moe_load=False, model=None, mpu=None, num_experts=1,

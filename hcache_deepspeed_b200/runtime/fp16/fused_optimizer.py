@@ -49,6 +49,50 @@ class _FP16Base:
     def get_global_grad_norm(self):
         return self._global_grad_norm
 
+    # ---- small public surface shared with the ZeRO wrappers (ref: fused_optimizer.py set_lr / get_lr /
+    #      override_loss_scale / unscale_and_clip_grads / initialize_optimizer_states) ----------------------------------
+    def set_lr(self, lr: float) -> None:
+        for g in self.optimizer.param_groups:
+            g["lr"] = lr
+
+    def get_lr(self) -> float:
+        return self.optimizer.param_groups[0]["lr"]
+
+    def override_loss_scale(self, loss_scale: float) -> None:
+        self.custom_loss_scaler = True
+        self.external_loss_scale = loss_scale
+
+    def unscale_and_clip_grads(self, grad_groups_flat, total_norm: float, apply_scale: bool = True) -> float:
+        """The divisor that removes the loss scale and clips to ``clip_grad`` in one pass; applied in place unless
+        ``apply_scale`` is false."""
+        combined = float(self.cur_scale)
+        if self.clip_grad > 0.0:
+            clip = (total_norm / self.cur_scale + 1e-6) / self.clip_grad
+            if clip > 1:
+                combined = clip * self.cur_scale
+        if apply_scale:
+            for g in grad_groups_flat:
+                g.data.mul_(1.0 / combined)
+        return combined
+
+    def initialize_optimizer_states(self) -> None:
+        """Create the inner optimizer's state tensors now (a step on zero gradients, masters restored afterwards)."""
+        masters = [m for m in getattr(self, "fp32_groups_flat", []) if m.numel()]
+        saved = [m.detach().clone() for m in masters]
+        for m in masters:
+            m.grad = torch.zeros_like(m)
+        self.optimizer.step()
+        for m, sv in zip(masters, saved):
+            m.grad = None
+            m.data.copy_(sv)
+        for st in self.optimizer.state.values():
+            if "step" in st:
+                st["step"] = st["step"] * 0 if torch.is_tensor(st["step"]) else 0
+
+    def step_fused_adam(self, closure=None):
+        """Legacy entry of the reference for its apex-style fused Adam; the regular ``step`` already is one fused pass."""
+        return self.step(closure)
+
     def _mp_reduce(self, v: float, op) -> float:
         if self.mpu is None or not dist.is_initialized():
             return v

@@ -69,8 +69,11 @@ def _engine_state_tensors(engine, kind: OffloadStateTypeEnum):
                 if torch.is_tensor(t) and t.dim() > 0 and not k.endswith("_offload_buffer")]
     if kind == OffloadStateTypeEnum.hp_params:
         return [t for t in (getattr(opt, "fp32_partitioned_groups_flat", None) or getattr(opt, "single_partition_of_fp32_groups", None)
-                            or []) if t.numel()]
+                            or getattr(opt, "fp32_groups_flat", None) or []) if t.numel()]
     if kind == OffloadStateTypeEnum.lp_params:
+        flats, _ = _flat_lp_layout(opt)
+        if flats is not None:      # parameters are views of flat buffers: the buffers move, the views are re-made
+            return [f for f in flats if f.numel()]
         out = []
         for p in engine.module.parameters():
             if is_zero_param(p):
@@ -88,6 +91,29 @@ def _engine_state_tensors(engine, kind: OffloadStateTypeEnum):
         buf = getattr(opt, "ipg_buffer", None) or getattr(opt, "_grad_flat", None)
         return [b for b in (buf if isinstance(buf, (list, tuple)) else [buf]) if torch.is_tensor(b)]
     return []
+
+
+def _flat_lp_layout(opt):
+    """(flat low-precision buffers, parameter lists) when the optimizer keeps its parameters as views of flat buffers
+    (ZeRO-1/2, bf16 and fp16 wrappers), else (None, None)."""
+    for flat_name, group_name in (("bit16_groups_flat", "bit16_groups"), ("fp16_groups_flat", "fp16_groups")):
+        flats, groups = getattr(opt, flat_name, None), getattr(opt, group_name, None)
+        if flats is not None and groups is not None:
+            return flats, groups
+    return None, None
+
+
+def _rebind_lp_views(opt) -> None:
+    """Point every parameter at its range of the (moved) flat buffer again."""
+    flats, groups = _flat_lp_layout(opt)
+    if flats is None:
+        return
+    for flat, params in zip(flats, groups):
+        off = 0
+        for p in params:
+            if flat.numel():
+                p.data = flat.data.narrow(0, off, p.numel()).view(p.shape)
+            off += p.numel()
 
 
 def offload_engine_states(engine, include=None, device=torch.device("cpu"), pin_memory: bool = True, non_blocking: bool = False) -> None:
@@ -110,6 +136,8 @@ def offload_engine_states(engine, include=None, device=torch.device("cpu"), pin_
             buf.copy_(t.data, non_blocking=non_blocking)
             record[id(t)] = (t, t.device, kind)
             t.data = buf
+    if OffloadStateTypeEnum.lp_params in kinds:
+        _rebind_lp_views(engine.optimizer)
     if torch.cuda.is_available() and not non_blocking:
         torch.cuda.synchronize()
         torch.cuda.empty_cache()
@@ -119,7 +147,10 @@ def reload_engine_states(engine, non_blocking: bool = False) -> None:
     record = engine.__dict__.get("_offloaded_states") or {}
     for t, home, _ in record.values():
         t.data = t.data.to(home, non_blocking=non_blocking) if t.data.device != home else t.data.clone()
+    touched_lp = any(kind == OffloadStateTypeEnum.lp_params for _, _, kind in record.values())
     record.clear()
+    if touched_lp:
+        _rebind_lp_views(engine.optimizer)
     if torch.cuda.is_available() and not non_blocking:
         torch.cuda.synchronize()
 

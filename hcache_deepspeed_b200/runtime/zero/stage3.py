@@ -21,6 +21,7 @@ import torch
 from ... import comm as dist
 from ...utils.logging import logger
 from ..fp16.loss_scaler import CreateLossScaler
+from .optimizer_api import ZeroOptimizerAPI
 from .partition_parameters import (Init, ZeroParamStatus, _partition_param, all_gather_params, is_zero_param, read_partition,
                                    release_partition, set_param_swapper, write_partition)
 
@@ -235,7 +236,7 @@ class DeepSpeedZeRoOffload:
         return self
 
 
-class DeepSpeedZeroOptimizer_Stage3:
+class DeepSpeedZeroOptimizer_Stage3(ZeroOptimizerAPI):
 
     def __init__(self, module: torch.nn.Module, init_optimizer, param_names=None, timers=None, ds_config=None,
                  static_loss_scale: float = 1.0, dynamic_loss_scale: bool = False, dynamic_loss_args=None,
@@ -566,6 +567,94 @@ class DeepSpeedZeroOptimizer_Stage3:
                 if p.ds_status == ZeroParamStatus.AVAILABLE:
                     p.ds_status = ZeroParamStatus.NOT_AVAILABLE
                     all_gather_params([p])
+
+    # ---- hooks of ZeroOptimizerAPI + the stage-3 part of the reference's public surface ---------------------------------
+    def _api_master_tensors(self):
+        return self.fp32_partitioned_groups_flat
+
+    def _api_local_grads(self):
+        return list(self.grad_partitions.values())
+
+    def _api_params(self):
+        return [p for g in self.fp16_groups for p in g]
+
+    @torch.no_grad()
+    def refresh_fp32_params(self) -> None:
+        """Low-precision partitions -> fp32 masters (after the partitions were written from outside, e.g. a module-only
+        load through ``GatheredParameters``); ref: stage3.py _restore_from_bit16_weights."""
+        with self._Resident(self):
+            for gi, params in enumerate(self.fp16_groups):
+                master, off = self.fp32_partitioned_groups_flat[gi], 0
+                for p in params:
+                    n = p.ds_partition_numel
+                    master.data.narrow(0, off, n).copy_(read_partition(p).detach().float().view(-1).to(master.device))
+                    release_partition(p)
+                    off += n
+
+    _restore_from_bit16_weights = refresh_fp32_params
+
+    def has_overflow(self, partition_gradients: bool = True) -> bool:
+        return self.check_overflow(partition_gradients)
+
+    def get_fp32_grad_partitions(self):
+        """``{group: {param index: this rank's fp32 gradient slice}}`` of the gradients reduced so far."""
+        out = {}
+        for gi, params in enumerate(self.fp16_groups):
+            for i, p in enumerate(params):
+                g = self.grad_partitions.get(p.ds_id)
+                if g is not None:
+                    out.setdefault(gi, {})[i] = g.float()
+        return out
+
+    def empty_partition_cache(self) -> None:
+        """Release every gathered, non-persistent parameter and forget the fetch trace's in-flight state."""
+        for g in self.fp16_groups:
+            for p in g:
+                if p.ds_status != ZeroParamStatus.NOT_AVAILABLE and not p.ds_persist:
+                    p.ds_active_sub_modules.clear()
+                    _partition_param(p)
+        off = self.parameter_offload
+        if hasattr(off, "_pos"):
+            off._pos = 0
+
+    def offload_states(self, include=None, device="cpu", pin_memory: bool = True, non_blocking: bool = False) -> None:
+        from .offload_states import offload_engine_states
+        offload_engine_states(self._engine_view(), include, torch.device(str(getattr(device, "value", device))), pin_memory,
+                              non_blocking)
+
+    def reload_states(self, non_blocking: bool = False) -> None:
+        from .offload_states import reload_engine_states
+        reload_engine_states(self._engine_view(), non_blocking)
+
+    def _engine_view(self):
+        """The (optimizer, module) pair the state-movement helpers work on, with their bookkeeping kept on this object."""
+        view = getattr(self, "_state_view", None)
+        if view is None:
+            import types
+            view = self._state_view = types.SimpleNamespace(optimizer=self, module=self.module)
+        return view
+
+    def quantize_nontrainable_params(self) -> None:
+        """ZeRO++ for frozen weights: from now on their all-gathers travel as int8 blocks (same wire format as qwZ)."""
+        for p in self.module.parameters():
+            if is_zero_param(p) and not p.requires_grad:
+                p.ds_quantized_gather = True
+
+    def checkpoint_event_prologue(self) -> None:
+        """Before a checkpoint is written: NVMe-resident optimizer state is brought into memory."""
+        self._ckpt_resident = self._Resident(self)
+        self._ckpt_resident.__enter__()
+
+    def checkpoint_event_epilogue(self) -> None:
+        res = getattr(self, "_ckpt_resident", None)
+        if res is not None:
+            res.__exit__(None, None, None)
+            self._ckpt_resident = None
+
+    def reset_swap_buffers(self) -> None:
+        sw = self.optimizer_swapper
+        if sw is not None and hasattr(sw, "reset_swap_buffers"):
+            sw.reset_swap_buffers()
 
     def get_fp32_state_dict_on_rank0(self):
         with self._Resident(self):

@@ -25,6 +25,7 @@ from ... import comm as dist
 from ...utils.logging import logger
 from ..fp16.loss_scaler import CreateLossScaler
 from ..utils import align_dense_tensors
+from .optimizer_api import ZeroOptimizerAPI
 
 SINGLE_PARTITION_OF_FP32_GROUPS = "single_partition_of_fp32_groups"
 BASE_OPTIMIZER_STATE = "base_optimizer_state"
@@ -42,7 +43,7 @@ def _comm_dtype(name):
             "fp32": torch.float32}.get(name, name)
 
 
-class DeepSpeedZeroOptimizer:
+class DeepSpeedZeroOptimizer(ZeroOptimizerAPI):
     """Wraps ``init_optimizer``; see module docstring. ``partition_grads=True`` selects stage 2."""
 
     def __init__(self, init_optimizer, param_names: Optional[dict] = None, timers=None, static_loss_scale: float = 1.0,
@@ -398,6 +399,54 @@ class DeepSpeedZeroOptimizer:
                 master.data.copy_(flat.narrow(0, self.rank * psize, psize).float().to(master.device))
 
     _restore_from_bit16_weights = refresh_fp32_params
+
+    # ---- hooks of ZeroOptimizerAPI + the stage-1/2 part of the reference's public surface -------------------------------
+    def _api_master_tensors(self):
+        return self.single_partition_of_fp32_groups
+
+    def _api_local_grads(self):
+        if any(g is not None for g in self.grad_partitions):
+            return [g for g in self.grad_partitions if g is not None]
+        return [p.grad for params in self.bit16_groups for p in params if p.grad is not None]
+
+    def _api_params(self):
+        return [p for params in self.bit16_groups for p in params]
+
+    def get_bit16_param_group(self, group_no: int):
+        """This rank's slice of group ``group_no``'s flat low-precision buffer."""
+        flat = self.bit16_groups_flat[group_no]
+        psize = flat.numel() // self.partition_count
+        return flat.narrow(0, self.rank * psize, psize)
+
+    def update_lp_params(self) -> None:
+        """Master weights -> low-precision parameters on every rank (what ``step`` does after the optimizer update; call
+        it after modifying the fp32 master copy by hand)."""
+        for gi, master in enumerate(self.single_partition_of_fp32_groups):
+            flat = self.bit16_groups_flat[gi]
+            if not flat.numel():
+                continue
+            own = self.get_bit16_param_group(gi)
+            own.copy_(master.detach().to(flat.device))
+            if self.partition_count > 1:
+                dist.all_gather_into_tensor(flat, own.clone(), group=self.dp_process_group)
+
+    def is_moe_group(self, group) -> bool:
+        return bool(group.get("moe", False))
+
+    def get_ep_ranks(self, rank: int = 0, group_name: Optional[str] = None):
+        from ...utils import groups
+        ep = groups._get_expert_parallel_group(group_name)
+        return list(range(dist.get_world_size(group=ep))) if ep is not None else [0]
+
+    def backward_prologue(self) -> None:
+        self.micro_step_id += 0     # accumulation bookkeeping lives in backward(); kept for callers that bracket it
+
+    def backward_epilogue(self) -> None:
+        pass
+
+    def print_rank_0(self, message) -> None:
+        if not dist.is_initialized() or dist.get_rank() == 0:
+            logger.info(message)
 
 
 def estimate_zero2_model_states_mem_needs(total_params: int, num_gpus_per_node: int = 1, num_nodes: int = 1,

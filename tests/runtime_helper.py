@@ -738,10 +738,12 @@ def engine_accessors_worker(rank, world, stage):
     out["kinds_after"] = len(offloaded_state_kinds(engine))
     engine.offload_states(include=[OffloadStateTypeEnum.optim_states, OffloadStateTypeEnum.hp_params], pin_memory=False)
     engine.reload_states()
-    l_round_trip = step(engine)
+    step(engine)
+    l_round_trip = step(engine)        # the second step after the round trip sees the first one's update
     torch.manual_seed(0)
     model2 = TinyNet(32)
     engine2, _, _, _ = ds.initialize(model=model2, config=cfg)
+    step(engine2)
     step(engine2)
     out["loss_pair"] = (l_round_trip, step(engine2))
     # partition cache + module state loading
@@ -761,6 +763,34 @@ def engine_accessors_worker(rank, world, stage):
         engine.load_module_state_dict({"module": sd})
         out["loaded"] = all(float((p.data.float() - 0.5).abs().max()) == 0.0 for p in engine.module.parameters())
         out["released"] = True
+    if stage >= 1:
+        # the fp32 masters were refreshed by the load too (else the next step would bring the old weights back)
+        opt = engine.optimizer
+        full = opt.get_full_hp_param(next(iter(engine.module.parameters())))
+        out["master_follows_load"] = float((full - 0.5).abs().max())
+        # optimizer-level public methods
+        opt.set_lr(0.125)
+        out["lr"] = (opt.get_lr(), engine.get_lr()[0])
+        loss = engine(x[lo:lo + 4], y[lo:lo + 4])
+        engine.backward(loss)
+        if stage < 2:
+            opt.reduce_gradients()
+        grads = opt._api_local_grads()
+        norm = opt.get_grad_norm_direct(grads)
+        out["overflow"] = opt.check_overflow()
+        p0 = next(iter(engine.module.parameters()))
+        g_full = opt.get_fp32_grad_for_param(p0)
+        out["grad_shape_ok"] = tuple(g_full.shape) == tuple(getattr(p0, "ds_shape", p0.shape))
+        engine.step()
+        out["norm_pair"] = (norm / opt.loss_scale, engine.get_global_grad_norm())
+        parts = opt.get_data_parallel_partitions(torch.arange(7))
+        out["parts"] = [t.tolist() for t in parts]
+        opt.override_loss_scale(4.0)
+        out["scale"] = opt.loss_scale
+        inside, outside, first = opt.get_partition_info([torch.zeros(3), torch.zeros(4), torch.zeros(5)], 6, 1)
+        out["pinfo"] = ([t.numel() for t in inside], [t.numel() for t in outside], first)
+        lean = opt.get_lean_optimizer_state()
+        out["lean_keys"] = sorted(k for k in lean[0] if k.startswith("exp_avg"))
     return out
 
 

@@ -661,7 +661,7 @@ def test_engine_config_getters_follow_the_config():
         getattr(bare, name)()
 
 
-@pytest.mark.parametrize("stage", [0, 2, 3])
+@pytest.mark.parametrize("stage", [0, 1, 2, 3])
 def test_engine_public_helpers_2ranks(stage):
     from tests.runtime_helper import engine_accessors_worker
     for r in run_distributed(engine_accessors_worker, 2, stage):
@@ -672,6 +672,11 @@ def test_engine_public_helpers_2ranks(stage):
         assert "optim_states" in r["kinds"] and "lp_params" in r["kinds"] and r["kinds_after"] == 0, r
         assert abs(r["loss_pair"][0] - r["loss_pair"][1]) < 1e-7, r
         assert r["released"] and r["loaded"], r
+        if stage >= 1:
+            assert r["master_follows_load"] == 0.0 and r["lr"] == (0.125, 0.125) and r["overflow"] is False, r
+            assert r["grad_shape_ok"] and r["norm_pair"][0] == pytest.approx(r["norm_pair"][1], rel=1e-5), r
+            assert r["parts"] == [[0, 1, 2, 3], [4, 5, 6]] and r["scale"] == 4.0, r
+            assert r["pinfo"] == ([4, 5], [3], 3) and r["lean_keys"] == ["exp_avg", "exp_avg_sq"], r
 
 
 def test_pipeline_engine_small_public_methods_2stages(tmp_path, monkeypatch):
