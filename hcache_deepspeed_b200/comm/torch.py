@@ -46,6 +46,21 @@ class TorchBackend(Backend):
     def has_reduce_scatter_tensor(cls) -> bool:
         return hasattr(tdist, "reduce_scatter_tensor")
 
+    @classmethod
+    def get_all_gather_function(cls):
+        return getattr(tdist, "all_gather_into_tensor", None) or getattr(tdist, "_all_gather_base", None)
+
+    @classmethod
+    def get_reduce_scatter_function(cls):
+        return getattr(tdist, "reduce_scatter_tensor", None) or getattr(tdist, "_reduce_scatter_base", None)
+
+    def all_gather_base(self, output_tensor, input_tensor, group=None, async_op=False):
+        """Older name of ``all_gather_into_tensor``."""
+        return self.get_all_gather_function()(output_tensor, input_tensor, group=group, async_op=async_op)
+
+    def broadcast_object_list(self, object_list, src, group=None, device=None):
+        return tdist.broadcast_object_list(object_list=object_list, src=src, group=group, device=device)
+
     def has_all_reduce_coalesced(self) -> bool:
         return hasattr(tdist, "all_reduce_coalesced")
 

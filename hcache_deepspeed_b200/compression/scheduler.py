@@ -33,6 +33,38 @@ class compression_scheduler:
         if on and not self.verbose[tech]:
             self.verbose[tech] = True
 
+    # ---- the reference's per-technique entry points (scheduler.py:33-170) ------------------------------------------------
+    def make_init(self) -> None:
+        """(Re)read the plan the model was prepared with: which modules each technique applies to."""
+        self.plan = getattr(self.model, "_compression_plan", [])
+        self.different_compression_methods = {
+            t: {"technique_enabled": bool(self.compression_config.get(t, {}).get("shared_parameters", {}).get("enabled", False)),
+                "shared_parameters": self.compression_config.get(t, {}).get("shared_parameters", {}),
+                "different_groups": [(name, params) for name, tech, params, _ in self.plan if tech == t]}
+            for t in TECHNIQUES}
+
+    def check_weight_quantization(self) -> None:
+        self._check("weight_quantization")
+
+    def check_activation_quantization(self) -> None:
+        self._check("activation_quantization")
+
+    def check_sparse_pruning(self) -> None:
+        self._check("sparse_pruning")
+
+    def check_head_pruning(self) -> None:
+        self._check("head_pruning")
+
+    def check_row_pruning(self) -> None:
+        self._check("row_pruning")
+
+    def check_channel_pruning(self) -> None:
+        self._check("channel_pruning")
+
+    def check_all_modules(self) -> None:
+        for t in TECHNIQUES:
+            self._check(t)
+
     def step(self, step_zero_check: bool = False):
         if not step_zero_check:
             self.training_steps += 1

@@ -30,6 +30,10 @@ class MultiNodeRunner(ABC):
     def get_cmd(self, environment: Dict[str, str], active_resources: Dict[str, List[int]]) -> List[str]:
         ...
 
+    def parse_user_args(self) -> List[str]:
+        """The user script's arguments as they go on the remote command line (PDSH quotes those with spaces)."""
+        return list(self.user_arguments)
+
     def add_export(self, key: str, var: str):
         self.exports[key.strip()] = var.strip()
 
@@ -60,7 +64,17 @@ class PDSHRunner(MultiNodeRunner):
         exports = "".join(f"export {k}={v}; " for k, v in self.exports.items())
         launch = self._launch_module() + ["--node_rank=%n"]
         return ["pdsh", "-S", "-f", str(PDSH_MAX_FAN_OUT), "-w", hosts, exports + f"cd {os.path.abspath('.')};",
-                *launch, self.user_script, *self.user_arguments]
+                *launch, self.user_script, *self.parse_user_args()]
+
+    def parse_user_args(self) -> List[str]:
+        """pdsh hands the command to a remote shell, which would split an argument at its spaces: such arguments are
+        wrapped in double quotes (embedded quotes escaped)."""
+        out = []
+        for arg in self.user_arguments:
+            if " " in arg:
+                arg = '"{}"'.format(arg.replace('"', '\\"'))
+            out.append(arg)
+        return out
 
 
 class _MPIStyle(MultiNodeRunner):

@@ -143,6 +143,41 @@ class AutoTP:
         return out
 
     @staticmethod
+    def kernel_supported(module_list) -> bool:
+        """True when one of the block types has a kernel-injection policy (then injection is the better route)."""
+        from .replace_policy import policy_class_names
+        return any(type(m).__name__ in policy_class_names for m in module_list)     # block class name -> family
+
+    def get_model_num_kv_heads(self, config):
+        """KV-head count under the names model configs use for it (falls back to the query-head count)."""
+        for name in ("multi_query_group_num", "num_kv_heads", "num_key_value_heads", "num_attention_heads", "n_heads",
+                     "attention_heads"):
+            v = getattr(config, name, None)
+            if v is not None:
+                return v
+        return None
+
+    def update_linear_policies(self) -> None:
+        """Which layer types ``_replace_module`` shards. ``linear_layer_setting`` (one or two types: linear[, embedding])
+        overrides the default of ``nn.Linear`` (+ HuggingFace ``Conv1D`` for GPT-2 blocks)."""
+        self.conv_linear_layer = False
+        if self.linear_layer_setting is not None:
+            setting = self.linear_layer_setting if isinstance(self.linear_layer_setting, (list, tuple)) else [self.linear_layer_setting]
+            self.linear_policies = {setting[0]: self._replace}
+            if len(setting) == 2:
+                self.linear_policies[setting[1]] = None      # embeddings stay replicated here (vocab-parallel is opt-in)
+        else:
+            self.linear_policies = {nn.Linear: self._replace}
+            if self.orig_layer_impl is not None and type(self.orig_layer_impl).__name__ == "type" and \
+                    self.orig_layer_impl.__name__ == "GPT2Block":
+                self.conv_linear_layer = True
+            try:
+                from transformers.pytorch_utils import Conv1D
+                self.linear_policies[Conv1D] = self._replace
+            except ImportError:
+                pass
+
+    @staticmethod
     def supported(model) -> bool:
         name = str(type(model)).lower()
         return not any(u in name for u in UNSUPPORTED)

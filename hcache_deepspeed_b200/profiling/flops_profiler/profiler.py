@@ -361,6 +361,13 @@ class FlopsProfiler:
                              f"{e.train_micro_batch_size_per_gpu() * getattr(e, 'dp_world_size', 1) / it:.2f}")
         return lines
 
+    def is_expert_tensor_parallelism_enabled(self) -> bool:
+        from ...moe.layer import MoE
+        for m in self.model.modules():
+            if isinstance(m, MoE) and hasattr(m, "enable_expert_tensor_parallelism"):
+                return bool(m.enable_expert_tensor_parallelism)
+        return False
+
     def print_model_profile(self, profile_step: int = 1, module_depth: int = -1, top_modules: int = 1, detailed: bool = True,
                             output_file: Optional[str] = None):
         """Summary, per-depth top modules and (``detailed``) the module tree with each module's share of parameters, MACs

@@ -153,6 +153,62 @@ class AsyncPartitionedParameterSwapper:
             self.aio_write_handle.wait()
             self.pending_writes = 0
 
+    # ---- direct-to-destination reads, buffers for partitions being built, fp32 -> lp file updates (ref: :329-422) ---------
+    def swap_into_buffer(self, param, dest_buffer: torch.Tensor) -> None:
+        """Read ``param``'s partition straight into ``dest_buffer`` when that is aligned (pinned where a GPU is present);
+        otherwise through a pool buffer, which is given back at once. The parameter itself stays NOT_AVAILABLE."""
+        assert param.ds_tensor.status == PartitionedParamStatus.NOT_AVAILABLE, f"param {param.ds_id} is already available or inflight"
+        numel = param.ds_tensor.ds_numel
+        direct = dest_buffer.numel() == self._aligned(numel) and dest_buffer.is_contiguous() and \
+            (dest_buffer.is_pinned() or not torch.cuda.is_available())
+        if direct:
+            self.aio_read_handle.async_pread(dest_buffer, self.get_path(param, must_exist=True))
+            self.aio_read_handle.wait()
+            return
+        buf = self._allocate(param)
+        self.aio_read_handle.async_pread(buf, self.get_path(param, must_exist=True))
+        self.aio_read_handle.wait()
+        dest_buffer.reshape(-1).narrow(0, 0, numel).copy_(buf.narrow(0, 0, numel))
+        self._release(param)
+
+    def get_buffer(self, param, numel: int) -> torch.Tensor:
+        """A pool buffer of ``numel`` elements assigned to ``param`` (to fill with a partition that is then swapped out)."""
+        pid = param.ds_id
+        assert self.available_buffer_ids, f"No swap buffers to allocate for fp16 param {pid} of numel = {numel}"
+        assert self._aligned(numel) <= self.elements_per_buffer, f"More elements {numel} than buffer size {self.elements_per_buffer}"
+        bid = self.available_buffer_ids.pop()
+        self.param_id_to_buffer_id[pid] = bid
+        self.param_id_to_numel[pid] = numel
+        swap = self.buffers.narrow(0, bid * self.elements_per_buffer, self._aligned(numel))
+        self.param_id_to_swap_buffer[pid] = swap
+        return swap.narrow(0, 0, numel)
+
+    def reserve_partitioned_swap_space(self, partition_num_elems) -> None:
+        """One staging area large enough for the (aligned) partitions listed: ``swap_out_partitioned_params`` converts
+        fp32 master slices into it and writes all files with one batch of requests."""
+        total = sum(self._aligned(n) for n in partition_num_elems)
+        buf = torch.zeros(total, dtype=self.dtype)
+        self.partitioned_swap_buffer = buf.pin_memory() if torch.cuda.is_available() else buf
+
+    def swap_out_partitioned_params(self, dst_fp16_params, src_fp32_params) -> None:
+        """After an optimizer step: the updated fp32 slices become the low-precision partition files of their parameters."""
+        assert getattr(self, "partitioned_swap_buffer", None) is not None, "partitioned swap buffers for fp16 params not initialized"
+        assert len(dst_fp16_params) == len(src_fp32_params), \
+            f"mismatch in number of fp16 params {len(dst_fp16_params)} and fp32 params {len(src_fp32_params)}"
+        self.synchronize_writes()
+        off = 0
+        for p, src in zip(dst_fp16_params, src_fp32_params):
+            n, span = src.numel(), self._aligned(src.numel())
+            assert off + span <= self.partitioned_swap_buffer.numel(), "reserved partitioned swap space is too small"
+            stage = self.partitioned_swap_buffer.narrow(0, off, span)
+            stage.narrow(0, 0, n).copy_(src.detach().reshape(-1))
+            self.aio_write_handle.async_pwrite(stage, self.get_path(p, must_exist=True))
+            self.pending_writes += 1
+            off += span
+        self.synchronize_writes()
+        for p in dst_fp16_params:
+            p.ds_tensor.status = PartitionedParamStatus.NOT_AVAILABLE
+
     def reserve_available_buffers(self) -> List[torch.Tensor]:
         return [self.buffers.narrow(0, b * self.elements_per_buffer, self.elements_per_buffer) for b in self.available_buffer_ids]
 

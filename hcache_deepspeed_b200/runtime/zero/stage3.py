@@ -235,6 +235,51 @@ class DeepSpeedZeRoOffload:
     def get_param_coordinator(self, training=True):
         return self
 
+    # ---- the reference's public names for the same steps (parameter_offload.py:200-520) --------------------------------
+    def setup_zero_stage3_hooks(self) -> None:
+        if not self.hooks:
+            self._install(self.module)
+
+    def partition_all_parameters(self) -> None:
+        """Release every gathered parameter that is not marked persistent."""
+        for p in self.module.parameters():
+            if is_zero_param(p) and not p.ds_persist and p.ds_status != ZeroParamStatus.NOT_AVAILABLE:
+                p.ds_active_sub_modules.clear()
+                _partition_param(p)
+
+    def empty_partition_cache(self) -> None:
+        self.partition_all_parameters()
+        self._pos = 0
+
+    def mark_persistent_parameters(self, param_threshold: int, model_threshold: int):
+        """Keep parameters of at most ``param_threshold`` elements resident, smallest-first in module order until
+        ``model_threshold`` elements in total are resident; returns the parameters newly made persistent (gathered)."""
+        budget = model_threshold - sum(p.ds_numel for p in self.module.parameters() if is_zero_param(p) and p.ds_persist)
+        newly = []
+        for p in self.module.parameters():
+            if not is_zero_param(p) or p.ds_persist or p.ds_numel > param_threshold:
+                continue
+            if p.ds_numel > budget:
+                continue
+            budget -= p.ds_numel
+            p.ds_persist = True
+            newly.append(p)
+        if newly:
+            all_gather_params(newly)
+        return newly
+
+    def pre_sub_module_forward_function(self, sub_module) -> None:
+        self._pre_forward(sub_module, None)
+
+    def post_sub_module_forward_function(self, sub_module) -> None:
+        self._release(sub_module)
+
+    def pre_sub_module_backward_function(self, sub_module) -> None:
+        self._pre_backward(sub_module, None)
+
+    def post_sub_module_backward_function(self, sub_module) -> None:
+        self._release(sub_module)
+
 
 class DeepSpeedZeroOptimizer_Stage3(ZeroOptimizerAPI):
 

@@ -78,3 +78,63 @@ def test_reshape_3d_maps_and_zero_checkpoint(tmp_path):
     assert sd["single_partition_of_fp32_groups"][0].numel() == 12
     c = R.clone_tensors_for_torch_save({"a": [torch.ones(4)[:2]]})
     assert c["a"][0].untyped_storage().size() == 8
+
+
+def test_deepspeed_checkpoint_2d_views_of_a_pipeline_checkpoint(tmp_path):
+    """Megatron-DeepSpeed layout (one file per layer and tensor-parallel slice + one model-states file per (pipe, tensor)
+    rank): the layer / stage maps and the merged states when opened under a smaller tp x pp (ref:
+    checkpoint/deepspeed_checkpoint.py:96-260)."""
+    import torch
+    from hcache_deepspeed_b200.checkpoint import DeepSpeedCheckpoint
+    tp, pp, blocks, h = 2, 2, 4, 4
+    g = torch.Generator().manual_seed(0)
+    full = {}
+    for layer in range(blocks + 2):
+        if layer == 0:
+            sd = {"word_embeddings.weight": torch.randn(8, h, generator=g), "position_embeddings.weight": torch.randn(6, h, generator=g)}
+        elif layer == blocks + 1:
+            sd = {"weight": torch.randn(h, generator=g), "bias": torch.randn(h, generator=g)}
+        else:
+            sd = {"input_layernorm.weight": torch.randn(h, generator=g),
+                  "self_attention.query_key_value.weight": torch.randn(3 * h, h, generator=g),
+                  "self_attention.dense.weight": torch.randn(h, h, generator=g),
+                  "self_attention.dense.bias": torch.randn(h, generator=g),
+                  "mlp.dense_h_to_4h.weight": torch.randn(4 * h, h, generator=g),
+                  "mlp.dense_4h_to_h.weight": torch.randn(h, 4 * h, generator=g)}
+        full[layer] = sd
+        for r in range(tp):
+            part = {}
+            for k, v in sd.items():
+                if k in ("input_layernorm.weight", "self_attention.dense.bias", "position_embeddings.weight") or layer == blocks + 1:
+                    part[k] = v.clone()
+                elif k in ("self_attention.dense.weight", "mlp.dense_4h_to_h.weight"):
+                    part[k] = v.chunk(tp, dim=1)[r].clone()
+                else:
+                    part[k] = v.chunk(tp, dim=0)[r].clone()
+            torch.save(part, tmp_path / f"layer_{layer:02d}-model_{r:02d}-model_states.pt")
+    for r in range(tp * pp):
+        torch.save({"iteration": 17, "args": {"hidden": h}, "checkpoint_info": {"v": 1}, "module": None}, tmp_path / f"mp_rank_{r:02d}_model_states.pt")
+
+    ck = DeepSpeedCheckpoint(str(tmp_path))
+    assert (ck.original_tp_degree, ck.original_pp_degree) == (2, 2) and ck.get_iteration() == 17 and ck.get_checkpoint_info() == {"v": 1}
+    assert ck.get_embedding_layer_id() == "layer_00" and ck.get_final_norm_layer_id() == "layer_05"
+    assert ck.get_pp_transformer_map(0) == ["layer_01", "layer_02"] and ck.get_pp_transformer_map(1) == ["layer_03", "layer_04"]
+    assert [len(f) for f in ck.transformer_file_map[(1, 0)]] == [1, 1]
+    st = ck.get_transformer_state(tp_index=1, pp_index=1)      # unchanged degrees: the slice files as they are
+    torch.testing.assert_close(st[0]["mlp.dense_4h_to_h.weight"], full[3]["mlp.dense_4h_to_h.weight"].chunk(2, dim=1)[1])
+
+    one = DeepSpeedCheckpoint(str(tmp_path), tp_degree=1, pp_degree=1)
+    assert one.is_change_tp_degree() and one.is_change_pp_degree() and not one.is_change_dp_degree()
+    assert len(one.get_embedding_files(0)) == 2 and len(one.get_final_norm_files(0)) == 2
+    emb = one.get_embedding_state(0)
+    torch.testing.assert_close(emb["word_embeddings.weight"], full[0]["word_embeddings.weight"])
+    torch.testing.assert_close(emb["position_embeddings.weight"], full[0]["position_embeddings.weight"])
+    torch.testing.assert_close(one.get_final_norm_state(0)["weight"], full[blocks + 1]["weight"])
+    layers = one.get_transformer_state(0, 0)
+    assert len(layers) == blocks and one.get_pp_transformer_map(0) == [f"layer_{i:02d}" for i in range(1, blocks + 1)]
+    for i, sd in enumerate(layers, start=1):
+        for k, v in full[i].items():
+            torch.testing.assert_close(sd[k], v)
+    assert [os.path.basename(f) for f in one.get_2d_parallel_files(0, 0)] == [f"mp_rank_{r:02d}_model_states.pt" for r in range(4)]
+    assert one.get_2d_parallel_state(0, 0)["iteration"] == 17
+    one.show_2d_mapping(); one.show_tp_embedding_map(); one.show_tp_final_norm_map(); one.show_pp_transformer_map(); one.show_transformer_file_map()

@@ -133,6 +133,24 @@ def test_nvme_swappers(tmp_path):
     sw.synchronize_reads()
     for p, w in zip(ps, want):
         assert torch.equal(p.ds_tensor.data, w)
+    # direct reads into a caller's buffer, updating the files from fp32 slices, a pool buffer for a new partition
+    sw.remove_partition_and_release_buffers(ps)
+    dest = torch.zeros(sw._aligned(5000))
+    sw.swap_into_buffer(ps[0], dest)
+    assert torch.equal(dest[:5000], want[0]) and sw.available_swap_in_buffers() == 3
+    odd = torch.zeros(5003)                                  # not aligned: goes through a pool buffer and gives it back
+    sw.swap_into_buffer(ps[1], odd)
+    assert torch.equal(odd[:5001], want[1]) and sw.available_swap_in_buffers() == 3
+    sw.reserve_partitioned_swap_space([5000, 5001])
+    new = [w.double() * 2 for w in want]
+    sw.swap_out_partitioned_params(ps, new)
+    sw.swap_in(ps, async_op=False)
+    for p, w in zip(ps, want):
+        assert torch.equal(p.ds_tensor.data, w * 2)
+    sw.remove_partition_and_release_buffers(ps)
+    extra = types.SimpleNamespace(ds_id=7, ds_tensor=torch.zeros(1))
+    buf = sw.get_buffer(extra, 1234)
+    assert buf.numel() == 1234 and sw.available_swap_in_buffers() == 2
     ats = AsyncTensorSwapper(aio_handle(4096, 8, False, True, 1), 256)
     ats.add_buffers([torch.empty(1 << 16) for _ in range(2)])
     ts = [torch.randn(3000) for _ in range(40)]

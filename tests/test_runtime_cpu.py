@@ -689,3 +689,36 @@ def test_pipeline_engine_small_public_methods_2stages(tmp_path, monkeypatch):
         assert r["loss_new_shape"] == res[0]["loss_new_shape"] and r["loss_ckpt"] == res[0]["loss_ckpt"]
         assert r["mem"] is None
     assert res[0]["files"] == ["layer_00-model_00-model_states.pt"] and res[1]["files"] == ["layer_02-model_00-model_states.pt"]
+
+
+def test_zero_offload_public_step_names():
+    """The reference's names for the fetch / release steps and persistence marking of ``DeepSpeedZeRoOffload``
+    (parameter_offload.py:200-520), driven by hand on a ZeRO-3 engine."""
+    import hcache_deepspeed_b200 as ds
+    from hcache_deepspeed_b200.runtime.zero import ZeroParamStatus
+    torch.manual_seed(0)
+    model = torch.nn.Sequential(torch.nn.Linear(8, 16), torch.nn.Tanh(), torch.nn.Linear(16, 2))
+    engine, _, _, _ = ds.initialize(model=model, config={
+        "train_micro_batch_size_per_gpu": 2, "optimizer": {"type": "SGD", "params": {"lr": 0.1}}, "steps_per_print": 1000,
+        "zero_optimization": {"stage": 3, "stage3_param_persistence_threshold": 0}})
+    off = engine.optimizer.parameter_offload
+    lin = model[0]
+    off.pre_sub_module_forward_function(lin)
+    assert all(p.ds_status == ZeroParamStatus.AVAILABLE for p in lin.parameters())
+    off.post_sub_module_forward_function(lin)
+    assert all(p.ds_status == ZeroParamStatus.NOT_AVAILABLE for p in lin.parameters())
+    off.pre_sub_module_backward_function(model[2])
+    off.partition_all_parameters()
+    assert all(p.ds_status == ZeroParamStatus.NOT_AVAILABLE for p in model.parameters())
+    newly = off.mark_persistent_parameters(param_threshold=16, model_threshold=20)
+    assert sorted(p.ds_numel for p in newly) == [2, 16] and all(p.ds_persist and p.ds_status == ZeroParamStatus.AVAILABLE for p in newly)
+    x = torch.randn(2, 8)
+    loss = engine(x).pow(2).mean()
+    engine.backward(loss)
+    engine.step()
+    assert all(p.ds_status == ZeroParamStatus.AVAILABLE for p in newly)         # persistent ones stay resident through a step
+    off.empty_partition_cache()
+    n_hooks = len(off.hooks)
+    off.destroy()
+    off.setup_zero_stage3_hooks()
+    assert len(off.hooks) == n_hooks
