@@ -14,6 +14,7 @@ import sys
 from typing import Callable, Dict, List, Optional
 
 from ..utils.logging import logger
+from .staged import StagedSearch
 from .tuner import GridSearchTuner, ModelBasedTuner, RandomTuner
 
 DEFAULT_TUNING_SPACE = {
@@ -47,14 +48,17 @@ def _merge(a: Dict, b: Dict) -> Dict:
     return out
 
 
-class Autotuner:
+class Autotuner(StagedSearch):
 
     def __init__(self, user_config: Dict, num_params: int, num_gpus: int = 1, gpu_memory_bytes: Optional[int] = None,
                  run_fn: Optional[Callable[[Dict], Optional[float]]] = None, results_dir: str = "autotuning_results",
                  exps_dir: str = "autotuning_exps", user_script: Optional[str] = None, user_args: Optional[List[str]] = None):
         self.user_config = copy.deepcopy(user_config)
         at = dict(self.user_config.get("autotuning", {}))
-        self.metric = at.get("metric", "throughput")
+        self._at = at
+        self._metric = at.get("metric", "throughput")
+        self.search = at.get("search", "staged")    # "staged": the reference's stage-by-stage walk; "flat": one tuner over all
+        self.model_info = at.get("model_info") if isinstance(at.get("model_info"), dict) and "num_params" in at.get("model_info", {}) else None
         self.tuner_type = at.get("tuner_type", "gridsearch")
         self.early_stopping = at.get("tuner_early_stopping", 5)
         self.num_trials = at.get("tuner_num_trials", 50)
@@ -132,26 +136,45 @@ class Autotuner:
             return None
         if not os.path.exists(metric_path):
             return None
-        return json.load(open(metric_path)).get(self.metric)
+        return json.load(open(metric_path)).get(self._metric)
+
+    def _launch_with_config(self, cfg: Dict, file_name: str) -> int:
+        os.makedirs(self.results_dir, exist_ok=True)
+        path = os.path.join(self.results_dir, file_name)
+        with open(path, "w") as f:
+            json.dump(cfg, f, indent=2)
+        cmd = [sys.executable, self.user_script, *self.user_args, "--deepspeed_config", path]
+        return subprocess.run(cmd, stdout=subprocess.DEVNULL, stderr=subprocess.DEVNULL).returncode
 
     def tune(self):
+        """Run the search (``autotuning.search``: "staged" - default - or "flat") and return the best config."""
+        if self.search == "staged":
+            if not self.feasible_stages():
+                logger.warning("autotuning: the model states do not fit on the device under any ZeRO stage")
+                return None
+            best = self.tune_staged()
+            logger.info(f"autotuning: best {self._metric} = {self.best_metric}")
+            return best
+        return self.tune_flat()
+
+    def tune_flat(self):
         exps = self.experiments()
         if not exps:
             logger.warning("autotuning: the model states do not fit on the device under any ZeRO stage")
             return None
         run = self.run_fn if self.run_fn is not None else self._run_script
         cls = {"gridsearch": GridSearchTuner, "random": RandomTuner, "model_based": ModelBasedTuner}[self.tuner_type]
-        tuner = cls(exps, run, self.metric)
+        tuner = cls(exps, run, self._metric)
         n = tuner.tune(sample_size=1, n_trials=self.num_trials, early_stopping=self.early_stopping)
         self.records["all"] = tuner.records
         self.best_config, self.best_metric = tuner.best_exp, tuner.best_metric_val
-        logger.info(f"autotuning: {n} experiments, best {self.metric} = {self.best_metric}")
+        logger.info(f"autotuning: {n} experiments, best {self._metric} = {self.best_metric}")
         return self.best_config
 
     def print_tuning_results(self):
         for exp, val in self.records.get("all", []):
             z = exp.get("zero_optimization", {}).get("stage", 0)
-            print(f"z{z} mbs={exp['train_micro_batch_size_per_gpu']:<5d} {self.metric}={val}")
+            print(f"z{z} mbs={exp['train_micro_batch_size_per_gpu']:<5d} {self._metric}={val}")
 
     def write_optimal_config(self, path: Optional[str] = None):
         if self.best_config is None:

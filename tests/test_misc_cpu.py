@@ -93,12 +93,54 @@ def test_autotuner_picks_best_feasible_config(tmp_path):
 
     for tuner in ("gridsearch", "random", "model_based"):
         a = Autotuner({"fp16": {"enabled": True}, "autotuning": {"tuner_type": tuner, "num_tuning_micro_batch_sizes": 4,
-                                                                  "tuner_early_stopping": 100}},
+                                                                  "tuner_early_stopping": 100, "search": "flat"}},
                       num_params=int(30e9), num_gpus=8, run_fn=run)
         assert a.feasible_stages() == [1, 2, 3]                              # 30B fp16 states: 600 GB unpartitioned
         best = a.tune()
         assert (best["zero_optimization"]["stage"], best["train_micro_batch_size_per_gpu"]) == (2, 8) and a.best_metric == 74
         assert os.path.exists(a.write_optimal_config(str(tmp_path / f"{tuner}.json")))
+
+
+def test_autotuner_staged_search_walks_stages_and_micro_batch_sizes(tmp_path):
+    """The reference's order of work: per ZeRO stage find the runnable micro-batch range (doubling + bisection around the
+    out-of-memory point), measure a short list up to the plateau, stop walking stages when one does not improve (fast)."""
+    from hcache_deepspeed_b200.autotuning import Autotuner
+    oom_above = {1: 12, 2: 40, 3: 100}
+    calls = []
+
+    def run(cfg):
+        z, mbs = cfg["zero_optimization"]["stage"], cfg["train_micro_batch_size_per_gpu"]
+        calls.append((z, mbs))
+        if mbs > oom_above[z]:
+            return None
+        return 1000.0 * mbs / (mbs + 8.0) - {1: 20.0, 2: 40.0, 3: 150.0}[z]   # saturating throughput, a cost per ZeRO stage
+
+    a = Autotuner({"fp16": {"enabled": True}, "gradient_accumulation_steps": 2,
+                   "autotuning": {"num_tuning_micro_batch_sizes": 4, "max_train_micro_batch_size_per_gpu": 256, "fast": True}},
+                  num_params=int(30e9), num_gpus=8, run_fn=run, user_args=["--bs", "16", "--lr=0.5"])
+    assert a.metric() == "throughput" and a.fast_enabled() and a.fp16_enabled() and a.mp_size() == 1
+    assert a.get_gas_from_user_config() == 2 and a.get_val_from_user_args("$--bs") == 16 and a.get_val_from_user_args("$--lr") == 0.5
+    assert a.get_instantiation_memory_required_per_gpu(3) < a.get_instantiation_memory_required_per_gpu(1) < a.get_gpu_memory_info()
+    assert a.get_tuning_micro_batch_size_list(1, 13, 4) == [1, 5, 9, 13] and a.get_tuning_micro_batch_size_list(4, 4, 3) == [4]
+    lo, hi = a.get_min_max_micro_batch_size(1, 1, 256)
+    assert lo == 1 and 10 <= hi <= 12                                   # 8 runs, 16 does not: bisected to within ~12 %
+    best = a.tune()
+    recs = a.get_best_space_records()
+    assert set(recs) == {"z1", "z2", "z3", "global"}
+    z1, z2, z3 = recs["z1"][1], recs["z2"][1], recs["z3"][1]
+    assert z2 > z1 and z2 > z3                                          # stage 2 wins: larger batches than 1, cheaper than 3
+    assert best["zero_optimization"]["stage"] == 2 and 30 <= best["train_micro_batch_size_per_gpu"] <= 40
+    assert best["gradient_accumulation_steps"] == 2 and a.best_metric == z2 == recs["global"][1]
+    assert 16 <= a.get_plateau_mbs("z2") <= best["train_micro_batch_size_per_gpu"]   # (over all sizes probed in z2)
+    assert all(m <= 256 for _, m in calls) and len(calls) < 60
+    assert os.path.exists(a.write_optimal_config(str(tmp_path / "best.json")))
+    # without fast mode the stage's other knobs are searched at the best micro-batch size
+    b = Autotuner({"fp16": {"enabled": True}, "zero_optimization": {"stage": 1},
+                   "autotuning": {"fast": False, "micro_batch_sizes": [2, 4], "tuner_num_trials": 4}},
+                  num_params=int(30e9), num_gpus=8, run_fn=run)
+    b.tune()
+    knob_runs = [e for e, v, _ in b.records["z1"] if "reduce_bucket_size" in e["zero_optimization"]]
+    assert len(knob_runs) == 4 and all(e["train_micro_batch_size_per_gpu"] == 4 for e in knob_runs)
 
 
 def test_onebit_compressed_allreduce_two_ranks():
