@@ -305,3 +305,50 @@ def test_engine_runs_random_ltd_schedule_and_checkpoints_it(tmp_path):
     assert fresh.random_ltd_scheduler.state_dict() == engine.random_ltd_scheduler.state_dict()
     for a, b in zip(fresh.module.parameters(), engine.module.parameters()):
         assert torch.equal(a, b)
+
+
+def test_sampler_clusters_unlock_with_difficulty_and_drain_without_replacement():
+    """Cluster scheme of the reference's sampler (data_sampler.py:171-340): a move of the difficulty forms a new cluster of
+    the newly eligible samples, batches draw from all clusters in proportion to size, each cluster is drained in a
+    shuffled order before any of its samples repeats; the stream resumes exactly from ``state_dict``."""
+    from hcache_deepspeed_b200.runtime.data_pipeline.data_sampler import DeepSpeedDataSampler
+    n = 240
+    diff = np.repeat(np.arange(1, 7), n // 6)                       # six difficulty levels, 40 samples each
+    cfg = {"seed": 5, "data_sampling": {"curriculum_learning": {"enabled": True, "curriculum_metrics": {"len": {
+        "difficulty_type": "value", "clustering_type": "schedule_based", "min_difficulty": 1, "max_difficulty": 6,
+        "schedule_type": "fixed_discrete", "schedule_config": {"difficulty": [1, 3, 6], "max_step": [4, 8]}}}}}}
+
+    def make():
+        return DeepSpeedDataSampler(cfg, n, micro_batch_size=5, data_parallel_rank=1, data_parallel_size=2,
+                                    gradient_accumulation_steps=2, difficulties={"len": diff})
+
+    s = make()
+    assert s.global_batch_size == 20 and s.get_start_end_idx() == (5, 10) and s.get_start_end_idx(7) == (4, 7)
+    assert s.get_sample_based_on_metric_value("len", 1, 3).tolist() == list(range(40, 120))
+    seen = []
+    for step in range(1, 5):                                        # difficulty 1: one cluster of 40 samples
+        b = s.get_next_global_batch()
+        assert diff[b].max() == 1
+        seen += b.tolist()
+    assert len(s.data_clusters) == 1 and len(set(seen[:40])) == 40 and set(seen[40:]) <= set(range(40))   # drained, then reshuffled
+    b = s.get_next_global_batch()                                   # step 5: difficulty 3 unlocks 80 more as a second cluster
+    assert s.data_cluster_sizes == [40, 80] and diff[b].max() <= 3
+    counts = np.zeros(2)
+    for _ in range(3):
+        counts += s.sample_from_clusters()
+    assert counts.sum() == 60 and counts[1] > counts[0]            # proportional to cluster size
+    state = s.state_dict()
+    nxt = [s.get_next_global_batch().tolist() for _ in range(5)]    # crosses into difficulty 6 (third cluster)
+    assert s.data_cluster_sizes == [40, 80, 120] and int(s._clustered.sum()) == n
+    r = make()
+    r.load_state_dict(state)
+    assert [r.get_next_global_batch().tolist() for _ in range(5)] == nxt
+    # percentile-based difficulty: the easiest k/max_difficulty of the data, whatever the metric's values are
+    pc = {"data_sampling": {"curriculum_learning": {"enabled": True, "curriculum_metrics": {"len": {
+        "difficulty_type": "percentile", "min_difficulty": 25, "max_difficulty": 100, "schedule_type": "fixed_discrete",
+        "schedule_config": {"difficulty": [25, 100], "max_step": [2]}}}}}}
+    p = DeepSpeedDataSampler(pc, n, micro_batch_size=10, data_parallel_rank=0, data_parallel_size=1, difficulties={"len": diff * 1000})
+    first = p.get_next_global_batch()
+    assert p.data_cluster_sizes == [50] and set(first.tolist()) <= set(np.argsort(diff, kind="stable")[:50].tolist())   # 25 % of 240 = 50 (2 per step)
+    micro = list(iter(make()))
+    assert len(micro) == (n // 20) * 2 and all(len(m) == 5 for m in micro)
