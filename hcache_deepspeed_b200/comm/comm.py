@@ -531,3 +531,28 @@ def init_distributed(dist_backend: Optional[str] = None, auto_mpi_discovery: boo
     tdist.init_process_group(backend=dist_backend, init_method=init_method, timeout=timeout,
                              rank=int(os.environ["RANK"]), world_size=int(os.environ["WORLD_SIZE"]), **kwargs)
     cdb = True
+
+
+# ---- remaining names of the reference's comm module (comm/comm.py) ---------------------------------------------------------
+ProcessGroup = torch.distributed.ProcessGroup
+
+
+def has_all_gather_into_tensor() -> bool:
+    return hasattr(torch.distributed, "all_gather_into_tensor")
+
+
+def has_reduce_scatter_tensor() -> bool:
+    return hasattr(torch.distributed, "reduce_scatter_tensor")
+
+
+def broadcast_object_list(object_list, src, group=None, device=None):
+    """Pickled Python objects from ``src`` to every rank of ``group`` (in place in ``object_list``)."""
+    return torch.distributed.broadcast_object_list(object_list, src=src, group=group, device=device)
+
+
+def init_deepspeed_backend(ds_backend=None, timeout=None, init_method=None):
+    """The reference selects one of its own (non-torch) backends here; this framework has one GPU backend (NCCL through
+    torch.distributed) plus the host engine, both reached through ``init_distributed`` - so this is that call."""
+    kw = {} if timeout is None else {"timeout": timeout}
+    return init_distributed(dist_backend=ds_backend or ("nccl" if torch.cuda.is_available() else "gloo"),
+                            init_method=init_method, **kw)

@@ -275,3 +275,12 @@ def required_torch_version(min_version=None, max_version=None) -> bool:
     if max_version is not None and v > pv.parse(str(max_version)):
         return False
     return True
+
+
+# ---- the rest of the reference's helper surface lives in utils_extra.py ----------------------------------------------------
+from .utils_extra import (DummyOptim, PartitionedTensor, TLinear, all_gather_dp_groups, all_gather_into_tensor_dp_groups,  # noqa: E402,F401
+                          compare_tensors_in_structures, copy_to_device, empty_cache, get_flattened_grad_norm, get_grad_zeros,
+                          get_inactive_params, get_ma_status, get_norm_with_moe_layers, get_norm_with_moe_layers_fast,
+                          get_weight_norm, graph_process, mask_nan_or_inf_with_val_inplace, memory_status, move_to_device,
+                          noop_context)
+from .zero.offload_states import offload_adam_states, reload_adam_states  # noqa: E402,F401

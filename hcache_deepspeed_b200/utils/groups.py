@@ -177,9 +177,55 @@ def _get_model_parallel_rank() -> int:
     return dist.get_rank(group=_MODEL_PARALLEL_GROUP) if _MODEL_PARALLEL_GROUP is not None else 0
 
 
+# ---- the mpu-style public names (the module itself can be handed to code that expects an ``mpu``; ref: groups.py:60-130) ----
+_tp_world_size_override = None
+_tp_rank_override = None
+
+
+def get_model_parallel_group():
+    return _get_model_parallel_group()
+
+
+def get_data_parallel_group():
+    return _get_data_parallel_group()
+
+
+def set_tensor_model_parallel_world_size(world_size) -> None:
+    """Pin the value ``get_tensor_model_parallel_world_size`` reports (``None`` = ask the group again)."""
+    global _tp_world_size_override
+    _tp_world_size_override = world_size
+
+
+def set_tensor_model_parallel_rank(rank) -> None:
+    global _tp_rank_override
+    _tp_rank_override = rank
+
+
+def get_model_parallel_world_size() -> int:
+    return _tp_world_size_override if _tp_world_size_override is not None else _get_model_parallel_world_size()
+
+
+def get_model_parallel_rank() -> int:
+    return _tp_rank_override if _tp_rank_override is not None else _get_model_parallel_rank()
+
+
+def get_tensor_model_parallel_src_rank() -> int:
+    """Global rank of the first member of this rank's tensor-parallel group."""
+    ws = get_model_parallel_world_size()
+    return (dist.get_rank() // ws) * ws if dist.is_initialized() else 0
+
+
+def get_data_parallel_world_size() -> int:
+    return _get_data_parallel_world_size()
+
+
+def get_data_parallel_rank() -> int:
+    return _get_data_parallel_rank()
+
+
 get_tensor_model_parallel_group = _get_model_parallel_group
-get_tensor_model_parallel_world_size = _get_model_parallel_world_size
-get_tensor_model_parallel_rank = _get_model_parallel_rank
+get_tensor_model_parallel_world_size = get_model_parallel_world_size
+get_tensor_model_parallel_rank = get_model_parallel_rank
 
 
 def _get_data_parallel_world_size() -> int:

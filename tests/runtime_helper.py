@@ -851,3 +851,42 @@ def pipe_api_worker(rank, world):
     engine.log_for_device("stage", engine.stage_id)
     out["mem"] = engine.mem_status("end")
     return out
+
+
+def runtime_utils_worker(rank, world):
+    """``PartitionedTensor`` round trips (even / uneven split, rebuilt from its wire form), per-group ZeRO all-gathers and
+    the mpu-style names of ``utils.groups`` (ref: runtime/utils.py:624-720, 961-1008; utils/groups.py:60-130)."""
+    import hcache_deepspeed_b200 as ds
+    from hcache_deepspeed_b200.runtime.utils import PartitionedTensor, all_gather_dp_groups, all_gather_into_tensor_dp_groups
+    from hcache_deepspeed_b200.utils import groups
+    ds.init_distributed(dist_backend="gloo")
+    out = {}
+    for name, shape in (("even", (4, 6)), ("uneven", (3, 5))):
+        full = torch.arange(shape[0] * shape[1], dtype=torch.float32).reshape(shape) + 1
+        pt = PartitionedTensor(full, group=None)
+        meta, local = pt.to_meta(), pt.data()
+        rebuilt = PartitionedTensor.from_meta(meta, local, group=None, device="cpu")
+        out[name] = (bool(torch.equal(pt.full(), full)), bool(torch.equal(rebuilt.full(), full)), int(local.numel()),
+                     list(rebuilt.full_size()))
+    flat = torch.zeros(8)
+    parts = list(flat.chunk(world))
+    parts[rank].fill_(float(rank + 1))
+    all_gather_into_tensor_dp_groups([flat], [parts], [None])
+    out["gathered"] = flat.tolist()
+    flat2 = torch.zeros(8)
+    parts2 = list(flat2.chunk(world))
+    parts2[rank].copy_(torch.arange(4.0) + 10 * rank)
+    all_gather_dp_groups([flat2], [parts2], [None], start_alignment_factor=1, allgather_bucket_size=4)
+    out["gathered_sharded"] = flat2.tolist()
+    out["mpu"] = (groups.get_model_parallel_world_size(), groups.get_model_parallel_rank(), groups.get_data_parallel_world_size(),
+                  groups.get_data_parallel_rank(), groups.get_tensor_model_parallel_src_rank())
+    groups.set_tensor_model_parallel_world_size(2)
+    groups.set_tensor_model_parallel_rank(rank)
+    out["mpu_pinned"] = (groups.get_tensor_model_parallel_world_size(), groups.get_tensor_model_parallel_rank(),
+                         groups.get_tensor_model_parallel_src_rank())
+    groups.set_tensor_model_parallel_world_size(None)
+    groups.set_tensor_model_parallel_rank(None)
+    objs = [{"a": rank}] if rank == 0 else [None]
+    ds.comm.broadcast_object_list(objs, src=0)
+    out["obj"] = objs[0]
+    return out

@@ -722,3 +722,45 @@ def test_zero_offload_public_step_names():
     off.destroy()
     off.setup_zero_stage3_hooks()
     assert len(off.hooks) == n_hooks
+
+
+def test_runtime_utils_helpers_single_process():
+    import math
+    from hcache_deepspeed_b200.runtime import utils as U
+    a, b = torch.nn.Parameter(torch.tensor([3.0, 0.0])), torch.nn.Parameter(torch.tensor([[4.0]]))
+    a.grad, b.grad = torch.tensor([0.0, 6.0]), torch.tensor([[8.0]])
+    assert U.get_weight_norm([a, b]) == pytest.approx(5.0) and U.get_weight_norm([a, b], norm_type=math.inf) == 4.0
+    assert U.get_flattened_grad_norm([a, b]) == pytest.approx(10.0) and U.get_grad_zeros([a, b]) == 1
+    assert U.get_flattened_grad_norm([a, b], grad_norm_mask=[[[1, 2]], []]) == pytest.approx(8.0)       # a's element 1 left out
+    assert U.get_norm_with_moe_layers(3.0, None, {}) == pytest.approx(3.0) and U.get_norm_with_moe_layers(-1, None, {}) == -1
+    t = torch.tensor([1.0, float("nan"), float("inf")])
+    U.mask_nan_or_inf_with_val_inplace(t)
+    assert t.tolist() == [1.0, -1.0, -1.0]
+    nest = {"x": [torch.ones(2), (torch.zeros(1), 5)], "y": "s"}
+    cp = U.copy_to_device(nest, "cpu", lambda t: True)
+    assert U.compare_tensors_in_structures(nest, cp) and cp is not nest and cp["x"] is not nest["x"]
+    assert U.move_to_device(nest, "cpu", lambda t: True)["x"][0] is nest["x"][0]
+    assert not U.compare_tensors_in_structures(nest, {"x": [torch.ones(2), (torch.ones(1), 5)], "y": "s"})
+    opt = U.DummyOptim([a, b])
+    opt.zero_grad()
+    assert a.grad is None and len(opt.param_groups[0]["params"]) == 2
+    from transformers.pytorch_utils import Conv1D
+    c = Conv1D(6, 4)                                    # weight stored [in=4, out=6]
+    lin = U.TLinear(c)
+    x = torch.randn(3, 4)
+    torch.testing.assert_close(lin(x), c(x))
+    calls = []
+    U.graph_process(False, lambda v: calls.append(v), torch.ones(1))       # CPU tensors: plain call
+    assert len(calls) == 1 and U.get_ma_status() == 0 and U.memory_status("x") is None
+    with U.noop_context():
+        pass
+
+
+def test_partitioned_tensor_and_group_names_2ranks():
+    from tests.runtime_helper import runtime_utils_worker
+    res = run_distributed(runtime_utils_worker, 2)
+    for rank, r in enumerate(res):
+        assert r["even"] == (True, True, 12, [4, 6]) and r["uneven"][:2] == (True, True) and r["uneven"][3] == [3, 5], r
+        assert r["gathered"] == [1.0] * 4 + [2.0] * 4 and r["gathered_sharded"] == [0.0, 1.0, 2.0, 3.0, 10.0, 11.0, 12.0, 13.0], r
+        assert r["mpu"] == (1, 0, 2, rank, rank) and r["mpu_pinned"] == (2, rank, 0) and r["obj"] == {"a": 0}, r
+    assert res[0]["uneven"][2] + res[1]["uneven"][2] == 15
