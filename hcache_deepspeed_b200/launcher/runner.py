@@ -20,6 +20,8 @@ import subprocess
 import sys
 from typing import Dict, List, Optional
 
+from ..utils.logging import logger
+
 DLTS_HOSTFILE = "/job/hostfile"
 EXPORT_ENVS = ["NCCL", "PYTHON", "MV2", "UCX", "HDS", "CUDA"]
 PDSH_MAX_FAN_OUT = 1024
@@ -30,7 +32,7 @@ def parse_args(args=None):
     p.add_argument("-H", "--hostfile", type=str, default=DLTS_HOSTFILE)
     p.add_argument("-i", "--include", type=str, default="")
     p.add_argument("-e", "--exclude", type=str, default="")
-    p.add_argument("--num_nodes", type=int, default=-1)
+    p.add_argument("--num_nodes", type=str, default="-1", help="N, or MIN:MAX with --elastic_training")
     p.add_argument("--min_elastic_nodes", type=int, default=-1)
     p.add_argument("--max_elastic_nodes", type=int, default=-1)
     p.add_argument("--num_gpus", "--num_accelerators", type=int, default=-1)
@@ -120,6 +122,36 @@ def parse_resource_filter(host_info: Dict[str, List[int]], include_str: str = ""
         if host in filtered:
             ordered[host] = filtered[host]
     return ordered
+
+
+def parse_node_config(node_config: str):
+    """``host`` -> (host, []); ``host:0,2`` -> (host, [0, 2])."""
+    if ":" not in node_config:
+        return node_config, []
+    hostname, slots = node_config.split(":")
+    return hostname, [int(x) for x in slots.split(",")]
+
+
+def parse_node_config_list(node_config_list: str) -> Dict[str, List[int]]:
+    """``host1:0,1@host2@host1:3`` -> {host1: [0, 1, 3], host2: []} (slots merged, sorted, de-duplicated)."""
+    out: Dict[str, List[int]] = collections.OrderedDict()
+    for node_config in node_config_list.split("@"):
+        hostname, slots = parse_node_config(node_config)
+        out.setdefault(hostname, [])
+        out[hostname] += slots
+    return {k: sorted(set(v)) for k, v in out.items()}
+
+
+def parse_num_nodes(str_num_nodes, elastic_training: bool):
+    """``--num_nodes``: ``N`` -> (N, -1); ``MIN:MAX`` (elastic training only) -> (MIN, MAX)."""
+    parts = str(str_num_nodes).split(":")
+    if len(parts) == 1:
+        return int(parts[0]), -1
+    if len(parts) == 2 and elastic_training:
+        return int(parts[0]), int(parts[1])
+    if len(parts) == 2:
+        raise RuntimeError("MIN:MAX format is only supported in elastic training")
+    raise RuntimeError(f"num_nodes {str_num_nodes} is not in MIN:MAX format")
 
 
 def parse_inclusion_exclusion(resource_pool, inclusion: str, exclusion: str):
@@ -257,10 +289,31 @@ def run_autotuning(args, active_resources) -> Optional[str]:
 
 def main(args=None):
     args = parse_args(args)
+    if args.elastic_training:
+        assert args.master_addr != "", "Master Addr is required when elastic training is enabled"
+    args.num_nodes, max_nodes = parse_num_nodes(args.num_nodes, args.elastic_training)
+    if args.elastic_training:
+        if args.min_elastic_nodes < 0:
+            args.min_elastic_nodes = args.num_nodes
+        if args.max_elastic_nodes < 0:
+            args.max_elastic_nodes = max_nodes if max_nodes > 0 else args.num_nodes
     resource_pool = fetch_hostfile(args.hostfile)
+    visible = os.environ.get("CUDA_VISIBLE_DEVICES", "")
+    if not resource_pool and visible:
+        # one node, devices restricted by the environment: keep that restriction unless explicit filters were given
+        if args.include or args.exclude or args.num_nodes > 1 or args.num_gpus > 0:
+            logger.info(f"Detected CUDA_VISIBLE_DEVICES={visible} but ignoring it because one or several of --include/"
+                        "--exclude/--num_gpus/--num_nodes cl args were used. If you want to use CUDA_VISIBLE_DEVICES don't pass "
+                        "any of these arguments to the launcher.")
+        else:
+            args.include = f"localhost:{visible}"
+            logger.info(f"Detected CUDA_VISIBLE_DEVICES={visible}: setting --include={args.include}")
+            del os.environ["CUDA_VISIBLE_DEVICES"]
     if not resource_pool:
         import torch
         n = args.num_gpus if args.num_gpus > 0 else max(1, torch.cuda.device_count())
+        if args.include.startswith("localhost:"):
+            n = max(n, max(parse_node_config(args.include)[1]) + 1)
         resource_pool = collections.OrderedDict(localhost=n)
         args.master_addr = args.master_addr or "127.0.0.1"
     active = parse_inclusion_exclusion(resource_pool, args.include, args.exclude)

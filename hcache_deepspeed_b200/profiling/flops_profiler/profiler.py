@@ -203,6 +203,55 @@ def number_to_string(num: float, units: Optional[str] = None, precision: int = 2
     return f"{num:.{precision}f} "
 
 
+# ---- formatting / per-module readers under the reference's names (profiler.py:1080-1200) ------------------------------------
+def macs_to_string(macs, units: Optional[str] = None, precision: int = 2) -> str:
+    return f"{number_to_string(macs, units=units, precision=precision)}MACs"
+
+
+def flops_to_string(flops, units: Optional[str] = None, precision: int = 2) -> str:
+    return f"{number_to_string(flops, units=units, precision=precision)}FLOPS"
+
+
+def bytes_to_string(b, units: Optional[str] = None, precision: int = 2) -> str:
+    return f"{number_to_string(b, units=units, precision=precision)}B"
+
+
+def params_to_string(params_num, units: Optional[str] = None, precision: int = 2) -> str:
+    units = units.replace("B", "G") if units else units
+    return number_to_string(params_num, units=units, precision=precision).replace("G", "B").strip()
+
+
+def duration_to_string(duration, units: Optional[str] = None, precision: int = 2) -> str:
+    """Seconds -> ``s`` / ``ms`` / ``us`` text."""
+    if units is None:
+        units = "s" if duration >= 1 else "ms" if duration >= 1e-3 else "us"
+    scale = {"s": 1.0, "ms": 1e3, "us": 1e6}[units]
+    return f"{round(duration * scale, precision):g} {units}"
+
+
+def get_module_flops(module: torch.nn.Module) -> int:
+    """FLOPs counted in ``module`` and everything below it during the profiled forward (the counters here are already
+    cumulative: an operator is credited to every module on the call stack)."""
+    return int(getattr(module, "__flops__", 0))
+
+
+def get_module_macs(module: torch.nn.Module) -> int:
+    return int(getattr(module, "__macs__", 0))
+
+
+def get_module_duration(module: torch.nn.Module) -> float:
+    """Wall time of ``module``'s forward; for a container that has no timing of its own, the sum of its children."""
+    d = float(getattr(module, "__duration__", 0.0))
+    return d if d > 0 else sum(get_module_duration(c) for c in module.children())
+
+
+def wrapFunc(func, funcFlopCompute):
+    """``func`` wrapped so that every call also adds ``funcFlopCompute(*args) -> (flops, macs)`` to the modules being
+    profiled; used to count an operator the profiler does not know."""
+    counter = lambda *a, **k: funcFlopCompute(*a, **k)     # noqa: E731
+    return _wrap(func, counter)
+
+
 class FlopsProfiler:
     """``prof = FlopsProfiler(model); prof.start_profile(); model(x); prof.stop_profile();
     prof.get_total_flops(); prof.print_model_profile(); prof.end_profile()``"""

@@ -254,3 +254,110 @@ def configure(mpu_, deepspeed_config=None, partition_activations: Optional[bool]
 
 def is_configured() -> bool:
     return _configured
+
+
+# ---- the reference's helper names around CheckpointFunction (checkpointing.py:68-480), over the functions above -----------
+def detach_variable(inputs, device=None):
+    """Detached copies of the tensors of a tuple (moved to ``device`` when given), keeping ``requires_grad``; non-tensors
+    pass through."""
+    if not isinstance(inputs, tuple):
+        raise RuntimeError(f"Only tuple of tensors is supported. Got Unsupported input type: {type(inputs).__name__}")
+    out = []
+    for inp in inputs:
+        if not torch.is_tensor(inp):
+            out.append(inp)
+            continue
+        req = inp.requires_grad
+        x = inp.to(device=device) if device is not None else inp
+        x = x.detach()
+        x.requires_grad = req
+        out.append(x)
+    return tuple(out)
+
+
+def get_partition_size(item: torch.Tensor) -> int:
+    """Elements of ``item`` one model-parallel rank keeps (the padded 1/mp share used by ``partition_activation``)."""
+    ws, _, _ = _mp_info()
+    return (item.numel() + ws - 1) // ws
+
+
+def get_partition_start(item: torch.Tensor) -> int:
+    _, rank, _ = _mp_info()
+    return rank * get_partition_size(item)
+
+
+def is_activation_to_checkpoint(item) -> bool:
+    """Floating-point tensors large enough to split over the model-parallel group, unless flagged ``no_checkpointing``."""
+    ws, _, _ = _mp_info()
+    return torch.is_tensor(item) and item.is_floating_point() and item.numel() >= ws and \
+        not getattr(item, "no_checkpointing", False)
+
+
+def extract_tensors(all_objects):
+    """Split a list / tuple into (tensors, non-tensors, flags) - ``flags[i]`` says whether position ``i`` was a tensor."""
+    tensors = [v for v in all_objects if torch.is_tensor(v)]
+    others = [v for v in all_objects if not torch.is_tensor(v)]
+    flags = [torch.is_tensor(v) for v in all_objects]
+    return (tuple(tensors), tuple(others), tuple(flags)) if isinstance(all_objects, tuple) else (tensors, others, flags)
+
+
+def merge_tensors(tensor_objects, non_tensor_objects, tensor_flags):
+    """Inverse of ``extract_tensors``. ``tensor_objects`` may also be the (partition, size) pair list a partitioned
+    checkpoint saves: then every tensor position takes two entries and the second is dropped."""
+    t_it, o_it = iter(tensor_objects), iter(non_tensor_objects)
+    paired = len(tensor_objects) == 2 * sum(bool(f) for f in tensor_flags) and len(tensor_objects) > 0
+    out = []
+    for is_tensor in tensor_flags:
+        if is_tensor:
+            out.append(next(t_it))
+            if paired:
+                next(t_it)
+        else:
+            out.append(next(o_it))
+    return tuple(out)
+
+
+def partition_activations(args, cpu_checkpoint: bool = False, contiguous_checkpoint: bool = False):
+    """What the forward of a partitioned checkpoint saves for ``args``: this rank's slice of each checkpointable tensor
+    (on the host under ``cpu_checkpoint``), other items as they are. ``contiguous_checkpoint`` is accepted for signature
+    parity - slices here are allocated by the caching allocator, which already places equal-sized blocks together."""
+    out = []
+    for item in args:
+        if not is_activation_to_checkpoint(item):
+            out.append(item)
+            continue
+        part = partition_activation(item)
+        out.append(part.cpu() if cpu_checkpoint else part)
+    return out
+
+
+def get_partitioned_activations_for_backward(args, inputs, contiguous_checkpoint: bool = False):
+    """The flat list ``[partition0, size0, partition1, size1, ...]`` kept for backward: the saved slice of every
+    checkpointable argument followed by its original shape as a tensor; other arguments followed by ``None``."""
+    out = []
+    for arg, inp in zip(args, inputs):
+        if not is_activation_to_checkpoint(arg):
+            out += [arg, None]
+            continue
+        out += [inp, torch.tensor(list(arg.shape), dtype=torch.long)]
+    return out
+
+
+def gather_partitioned_activations(tensors, device=None):
+    """Inverse of the above: every (slice, shape) pair is all-gathered over the model-parallel group and reshaped."""
+    assert len(tensors) % 2 == 0, f"Expected even count of tensors, instead got {len(tensors)}"
+    out = []
+    for item, size in zip(tensors[0::2], tensors[1::2]):
+        if size is None or not torch.is_tensor(item):
+            out.append(item)
+            continue
+        dev = device if device is not None else (item.device if item.device.type != "cpu" or not torch.cuda.is_available()
+                                                 else torch.device("cuda", torch.cuda.current_device()))
+        full = gather_partitioned_activation(item, [int(s) for s in size.tolist()], dev)
+        out.append(full)
+    return tuple(out)
+
+
+def get_cpu_activations_for_backward(args, inputs):
+    """Under CPU checkpointing without partitioning: the host copies replace the checkpointable arguments."""
+    return [inp if is_activation_to_checkpoint(arg) else arg for arg, inp in zip(args, inputs)]

@@ -260,3 +260,78 @@ def add_tuning_arguments(parser: argparse.ArgumentParser):
     g.add_argument("--warmup_num_steps", type=int, default=1000)
     g.add_argument("--warmup_type", type=str, default=WARMUP_LOG_RATE)
     return parser
+
+
+# ---- schedule configs from command-line arguments (ref: lr_schedules.py:124-253) --------------------------------------------
+_ARG_NAMES = {
+    LR_RANGE_TEST: ("lr_range_test_min_lr", "lr_range_test_step_rate", "lr_range_test_step_size", "lr_range_test_staircase"),
+    ONE_CYCLE: ("cycle_first_step_size", "cycle_first_stair_count", "cycle_second_step_size", "cycle_second_stair_count",
+                "decay_step_size", "cycle_min_lr", "cycle_max_lr", "decay_lr_rate", "cycle_min_mom", "cycle_max_mom",
+                "decay_mom_rate"),
+    WARMUP_LR: ("warmup_min_lr", "warmup_max_lr", "warmup_num_steps", "warmup_type"),
+}
+
+
+def parse_arguments():
+    """(namespace of the tuning arguments, the arguments it did not recognise) from ``sys.argv``."""
+    parser = add_tuning_arguments(argparse.ArgumentParser())
+    return parser.parse_known_args()
+
+
+def _override(args, params: dict, names) -> None:
+    for name in names:
+        value = getattr(args, name, None)
+        if value is not None:
+            params[name] = value
+
+
+def override_lr_range_test_params(args, params: dict) -> None:
+    _override(args, params, _ARG_NAMES[LR_RANGE_TEST])
+
+
+def override_1cycle_params(args, params: dict) -> None:
+    _override(args, params, _ARG_NAMES[ONE_CYCLE])
+
+
+def override_warmupLR_params(args, params: dict) -> None:
+    _override(args, params, _ARG_NAMES[WARMUP_LR])
+
+
+def override_params(args, params: dict) -> None:
+    """Every tuning argument present on ``args`` replaces the same-named entry of ``params``."""
+    for names in _ARG_NAMES.values():
+        _override(args, params, names)
+
+
+def get_config_from_args(args):
+    """(``{"type": ..., "params": {...}}``, None) for ``--lr_schedule``, or (None, reason)."""
+    name = getattr(args, LR_SCHEDULE, None)
+    if name is None:
+        return None, f"--{LR_SCHEDULE} not specified on command line"
+    if name not in VALID_LR_SCHEDULES:
+        return None, f"{name} is not supported LR schedule"
+    config = {"type": name, "params": {}}
+    _override(args, config["params"], _ARG_NAMES.get(name, _ARG_NAMES[WARMUP_LR]))
+    return config, None
+
+
+def get_lr_from_config(config):
+    """The learning rate a schedule config starts from / peaks at: (lr, "") or (None, reason)."""
+    if "type" not in config:
+        return None, "LR schedule type not defined in config"
+    if "params" not in config:
+        return None, "LR schedule params not defined in config"
+    name, params = config["type"], config["params"]
+    if name not in VALID_LR_SCHEDULES:
+        return None, f"{name} is not a valid LR schedule"
+    if name == LR_RANGE_TEST:
+        return params["lr_range_test_min_lr"], ""
+    if name == ONE_CYCLE:
+        return params["cycle_max_lr"], ""
+    return params["warmup_max_lr"], ""
+
+
+def update_lr(param_groups, lrs):
+    for group, lr in zip(param_groups, lrs):
+        group["lr"] = lr
+    return [group["lr"] for group in param_groups]

@@ -24,6 +24,39 @@ def test_zero_to_fp32_consolidates_shards(stage, tmp_path):
     assert os.path.exists(out) and set(torch.load(out, weights_only=False)) >= set(states[0])
     ck = DeepSpeedCheckpoint(os.path.join(d, "t3"))
     assert ck.original_dp_degree == 2 and ck.original_tp_degree == 1 and len(ck.zero_files) == 2
+    # lazy mode hands out descriptions that materialise one by one; a small shard limit gives numbered files + an index
+    from hcache_deepspeed_b200.checkpoint.zero_to_fp32 import (GatheredTensor, get_model_state_files, get_optim_files,
+                                                                natural_keys, parse_model_states, parse_optim_states,
+                                                                to_torch_tensor, zero3_partitioned_param_info)
+    lazy = get_fp32_state_dict_from_zero_checkpoint(d, tag="t3", lazy_mode=True)
+    assert any(isinstance(v, GatheredTensor) for v in lazy.values())
+    full = to_torch_tensor(lazy)
+    for k, v in states[0].items():
+        torch.testing.assert_close(full[k], v, rtol=1e-6, atol=1e-7)
+    assert all(v.numel() == 0 or v.shape == full[k].shape for k, v in to_torch_tensor(lazy, return_empty_tensor=True).items())
+    import json
+    for safe in (False, True):
+        idx = convert_zero_checkpoint_to_fp32_state_dict(d, str(tmp_path / f"sharded{int(safe)}"), max_shard_size="3KB", tag="t3",
+                                                         safe_serialization=safe)
+        meta = json.load(open(idx))
+        files = sorted(set(meta["weight_map"].values()))
+        assert idx.endswith(".index.json") and len(files) > 1 and set(meta["weight_map"]) >= set(states[0])
+        merged = {}
+        for f in files:
+            path = os.path.join(os.path.dirname(idx), f)
+            if safe:
+                from safetensors.torch import load_file
+                merged.update(load_file(path))
+            else:
+                merged.update(torch.load(path, weights_only=False))
+        for k, v in states[0].items():
+            torch.testing.assert_close(merged[k], v, rtol=1e-6, atol=1e-7)
+    tag_dir = os.path.join(d, "t3")
+    got_stage, world, flats = parse_optim_states(get_optim_files(tag_dir), tag_dir)
+    assert (got_stage, world, len(flats)) == (stage, 2, 2)
+    ms = parse_model_states(get_model_state_files(tag_dir))
+    assert ms[0].param_shapes and isinstance(ms[0].shared_params, dict)
+    assert zero3_partitioned_param_info(10, 4) == (3, 2) and sorted(["r10", "r2"], key=natural_keys) == ["r2", "r10"]
 
 
 def test_universal_checkpoint_resumes_with_other_dp_degree(tmp_path):

@@ -1088,3 +1088,14 @@ def test_elasticity_block_drives_the_batch_size_triple():
         DeepSpeedConfig({"elasticity": el, "train_batch_size": 8}, world_size=2)
     c = DeepSpeedConfig({"elasticity": dict(el, ignore_non_elastic_batch_info=True), "train_batch_size": 8}, world_size=2)
     assert c.train_batch_size == 1680
+
+
+def test_launcher_node_config_and_num_nodes_parsing():
+    from hcache_deepspeed_b200.launcher.runner import parse_node_config, parse_node_config_list, parse_num_nodes
+    assert parse_node_config("w0") == ("w0", []) and parse_node_config("w1:0,2") == ("w1", [0, 2])
+    assert parse_node_config_list("w1:2,0@w0@w1:3,0") == {"w1": [0, 2, 3], "w0": []}
+    assert parse_num_nodes("4", False) == (4, -1) and parse_num_nodes("2:8", True) == (2, 8) and parse_num_nodes(-1, False) == (-1, -1)
+    with pytest.raises(RuntimeError):
+        parse_num_nodes("2:8", False)
+    with pytest.raises(RuntimeError):
+        parse_num_nodes("1:2:3", True)
