@@ -3,6 +3,8 @@ from __future__ import annotations
 
 import copy
 import itertools
+import json
+import os
 import re
 from typing import Dict, List, Optional
 
@@ -124,3 +126,139 @@ def number_to_string(n: float, postfix: str = "", units=None, precision: int = 2
         if (units is None and n >= scale) or units == unit:
             return f"{round(n / scale, precision)} {unit}{postfix}"
     return f"{n} {postfix}".strip()
+
+
+# ---- template substitution, config merging / pruning, experiment files (ref: autotuning/utils.py:41-130, 181-290, 387-415) ----
+def find_replace_str(value, replace_dict: Dict):
+    """Substitute ``$name`` placeholders of a string from ``replace_dict`` (case-insensitive names; ``$nvme_path`` is left
+    for the runtime). A placeholder whose value is not a string replaces the WHOLE value (it must then stand alone)."""
+    if not isinstance(value, str):
+        return str(value)
+    found = re.findall(r"\$[\w]+", value)
+    for var in found:
+        key = var[1:].lower()
+        if key == "nvme_path":
+            continue
+        assert key in replace_dict, f"unknown var key: {key}, in {replace_dict}"
+        if isinstance(replace_dict[key], str):
+            value = value.replace(var, replace_dict[key])
+        else:
+            assert len(found) == 1, "unable to replace multiple non-string matches"
+            value = replace_dict[key]
+    return value
+
+
+def find_replace(target, replace_dict: Dict) -> None:
+    """In-place placeholder substitution through nested dicts / lists."""
+    if isinstance(target, dict):
+        for k, v in target.items():
+            if isinstance(v, str):
+                target[k] = find_replace_str(v, replace_dict)
+            elif isinstance(v, list):
+                for i in range(len(v)):
+                    v[i] = find_replace_str(v[i], replace_dict)
+            elif isinstance(v, dict):
+                find_replace(v, replace_dict)
+    elif isinstance(target, list):
+        for i in range(len(target)):
+            target[i] = str(find_replace_str(target[i], replace_dict))
+
+
+def get_list(val) -> list:
+    return val if isinstance(val, list) else [val]
+
+
+def combine_dict(d: Dict, u: Dict) -> Dict:
+    """Merge ``u`` into ``d``: nested dicts merge, a key present in both becomes the list of distinct values (a tuning axis)."""
+    for k, v in u.items():
+        if isinstance(v, dict):
+            d[k] = combine_dict(d.get(k, {}), v)
+        elif k not in d:
+            d[k] = v
+        else:
+            if not isinstance(d[k], list):
+                d[k] = [d[k]]
+            d[k].extend(x for x in get_list(v) if x not in d[k])
+    return d
+
+
+def del_if_exists(t: str, d: Dict) -> None:
+    """Delete key ``t`` at the first level it occurs on each branch of a nested dict."""
+    if t in d:
+        del d[t]
+        return
+    for v in d.values():
+        if isinstance(v, dict):
+            del_if_exists(t, v)
+
+
+def fetch_hostfile(hostfile_path: str):
+    """``{host: slots}`` of a hostfile (``None`` when the file does not exist)."""
+    from ..launcher.runner import fetch_hostfile as _fetch
+    return _fetch(hostfile_path)
+
+
+def validate_ds_config(config: Dict) -> bool:
+    """Screens out configs that cannot run: ZeRO-2 with both legacy offload switches, ZeRO-3 offload without a
+    DeepSpeed-built optimizer."""
+    zero = config.get("zero_optimization") or {}
+    stage = zero.get("stage")
+    if not zero or stage not in (2, 3):
+        return True
+    if stage == 2:
+        return not (zero.get("cpu_offload") and zero.get("cpu_offload_params"))
+    offload = any((zero.get(k) or {}).get("device") in ("cpu", "nvme") for k in ("offload_optimizer", "offload_param"))
+    return not (offload and not config.get("optimizer"))
+
+
+def remove_dupe_dicts(items: List[Dict]) -> List[Dict]:
+    """Distinct (nested) dicts of a list, first occurrences kept in order."""
+    seen, out = set(), []
+    for d in items:
+        key = json.dumps(d, sort_keys=True)
+        if key not in seen:
+            seen.add(key)
+            out.append(json.loads(key))
+    return out
+
+
+def prune_config(config: Dict, ignored_keys=()) -> None:
+    """Delete the sections named in ``ignored_keys`` wherever they first occur (in place)."""
+    for k in ignored_keys or ():
+        del_if_exists(k, config)
+
+
+def get_tuning_keys(tuning_space: Dict) -> List[str]:
+    """Names of the entries that offer more than one value."""
+    keys = []
+    for k, v in tuning_space.items():
+        if isinstance(v, dict):
+            keys.extend(get_tuning_keys(v))
+        elif isinstance(v, list) and len(v) > 1:
+            keys.append(k)
+    return keys
+
+
+def get_first_config(config: Dict):
+    """The config obtained by taking the first value of every list (the ``optimizer`` section is kept as given)."""
+    if not config:
+        return None
+    cfg = copy.deepcopy(config)
+    for k, v in cfg.items():
+        if isinstance(v, dict) and k != "optimizer":
+            cfg[k] = get_first_config(v)
+        elif isinstance(v, list) and v:
+            cfg[k] = v[0]
+    return cfg
+
+
+def write_experiments(exps: List[Dict], exps_dir: str) -> List[str]:
+    """One ``<name>.json`` per experiment description; returns the paths."""
+    os.makedirs(exps_dir, exist_ok=True)
+    paths = []
+    for exp in exps:
+        path = os.path.join(exps_dir, f"{exp['name']}.json")
+        with open(path, "w") as f:
+            json.dump(exp, f)
+        paths.append(path)
+    return paths

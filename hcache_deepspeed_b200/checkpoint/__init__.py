@@ -9,3 +9,4 @@ from .zero_to_fp32 import (convert_zero_checkpoint_to_fp32_state_dict, get_fp32_
                            load_state_dict_from_zero_checkpoint)
 from .reshape import (ZeROCheckpoint, get_model_3d_descriptor, meg_2d_parallel_map, model_3d_desc,  # noqa: F401
                       reshape_meg_2d_parallel)
+from .reshape import clone_tensors_for_torch_save  # noqa: F401,E402

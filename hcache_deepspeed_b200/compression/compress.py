@@ -5,6 +5,7 @@ Reference: ``deepspeed/compression/compress.py:100-240``, ``helper.py``, ``confi
 from __future__ import annotations
 
 import json
+import os
 import re
 from typing import Dict, List, Optional
 
@@ -18,6 +19,23 @@ from .scheduler import TECHNIQUES
 WEIGHT_QUANTIZATION, ACTIVATION_QUANTIZATION = "weight_quantization", "activation_quantization"
 SPARSE_PRUNING, ROW_PRUNING, HEAD_PRUNING, CHANNEL_PRUNING, LAYER_REDUCTION = ("sparse_pruning", "row_pruning", "head_pruning",
                                                                               "channel_pruning", "layer_reduction")
+
+
+def check_deepspeed_config(config):
+    """A config dict as is, a path to a JSON file loaded (duplicate keys are an error)."""
+    if isinstance(config, dict):
+        return config
+    if isinstance(config, str) and os.path.exists(config):
+        def no_dupes(pairs):
+            out = {}
+            for k, v in pairs:
+                if k in out:
+                    raise ValueError(f"Duplicate key in DeepSpeed config: {k}")
+                out[k] = v
+            return out
+        with open(config) as f:
+            return json.load(f, object_pairs_hook=no_dupes)
+    raise ValueError(f"Expected a string path to an existing deepspeed config, or a dictionary. Received: {config}")
 
 
 def get_compression_config(ds_config) -> Dict:
@@ -158,3 +176,6 @@ def redundancy_clean(model: nn.Module, deepspeed_config, mpu=None) -> nn.Module:
         elif tech == CHANNEL_PRUNING and getattr(m, "channel_pruning_method", None):
             m.fix_channel_pruning_helper(dim_reduction=dim_red)
     return model
+
+
+from .helper import get_compress_methods, get_module_name  # noqa: E402,F401  (the reference exports them from here too)

@@ -90,3 +90,59 @@ def register_on_step_begin(model: nn.Module):
         for p in getattr(module, "pruners", []):
             p.on_step_begin(0)
     return model.register_forward_pre_hook(hook)
+
+
+# ---- the reference's remaining helper names (compression/helper.py:185-322) -----------------------------------------------
+def compression_preparation(model: nn.Module, compression_technique_list, mpu=None) -> nn.Module:
+    """Swap every compressible layer for its compressible twin, then switch on the techniques of
+    ``compression_technique_list`` - entries ``(module name lists, related modules, {technique: parameters})`` as
+    ``get_compress_methods`` returns them."""
+    from .compress import _apply_technique
+    for name, module in list(model.named_modules()):
+        if name and is_module_compressible(module, mpu):
+            module_replacement(model, name, mpu=mpu)
+    for module_name_lists, _, technique in compression_technique_list:
+        for names in module_name_lists:
+            for name in names:
+                layer = recursive_getattr(model, name)
+                for tech, params in technique.items():
+                    shared = {k: v for k, v in params.items() if k != "params"}
+                    _apply_technique(layer, tech, shared, params.get("params", params))
+    return model
+
+
+def fix_compression(model: nn.Module, module_name: str, compression_technique: dict, mask=None, dim_reduction: bool = False):
+    """Make one module's compression permanent (quantised weights written back, pruned rows / heads / channels removed
+    when ``dim_reduction``); returns the mask the next layer needs, if any."""
+    module = recursive_getattr(model, module_name)
+    for tech, v in compression_technique.items():
+        on = bool(v.get("enabled", False))
+        if tech == "weight_quantization" and on and v.get("quantize_weight_in_forward", False):
+            return module.fix_weight_quantization()
+        if tech == "sparse_pruning" and on:
+            return module.fix_sparse_pruning_helper()
+        if tech == "row_pruning" and (on or mask is not None):
+            return module.fix_row_col_pruning_helper(mask, dim_reduction=dim_reduction)
+        if tech == "head_pruning" and (on or mask is not None):
+            return module.fix_head_pruning_helper(mask, v.get("num_heads"), dim_reduction=dim_reduction)
+        if tech == "channel_pruning" and (on or mask is not None):
+            return module.fix_channel_pruning_helper(mask, dim_reduction=dim_reduction)
+    return None
+
+
+def rewrite_optimizer_step(opt):
+    """Bracket ``opt.step`` with the ``on_before_optimizer_step`` / ``on_after_optimizer_step`` calls of the pruners hung
+    on ``opt.pruners`` (the original step stays reachable as ``opt.orig_step``)."""
+    import types
+
+    def new_step(self, closure=None):
+        for pruner in getattr(self, "pruners", []):
+            pruner.on_before_optimizer_step()
+        res = self.orig_step(closure) if closure is not None else self.orig_step()
+        for pruner in getattr(self, "pruners", []):
+            pruner.on_after_optimizer_step()
+        return res
+
+    opt.orig_step = opt.step
+    opt.step = types.MethodType(new_step, opt)
+    return opt

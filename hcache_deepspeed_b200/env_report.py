@@ -64,9 +64,83 @@ def debug_report():
     return rows
 
 
-def cli_main():
-    op_report()
-    debug_report()
+def ninja_installed() -> bool:
+    try:
+        import ninja  # noqa: F401
+        return True
+    except ImportError:
+        return shutil.which("ninja") is not None
+
+
+def nvcc_version():
+    """Release string of the nvcc that would build the ops (e.g. ``"12.9"``), or ``None`` without one."""
+    nvcc = shutil.which("nvcc") or "/usr/local/cuda/bin/nvcc"
+    if not os.path.exists(nvcc):
+        return None
+    out = subprocess.run([nvcc, "-V"], capture_output=True, text=True).stdout
+    for tok in out.split():
+        if tok.endswith(",") and tok[:-1].replace(".", "").isdigit() and "release" in out.split()[out.split().index(tok) - 1]:
+            return tok[:-1]
+    return None
+
+
+def installed_cann_path():
+    """Ascend toolkits are not a target of this framework (sm_100a only); kept so callers of the reference's report work."""
+    return None
+
+
+def installed_cann_version():
+    return None
+
+
+def get_shm_size():
+    """(bytes of /dev/shm, warnings): the host collectives engine and PyTorch data-loader workers live there."""
+    try:
+        st = os.statvfs("/dev/shm")
+    except OSError:
+        return None, ["/dev/shm is not available"]
+    size = st.f_frsize * st.f_blocks
+    warn = []
+    if size < 512 * 1024 ** 2:
+        warn.append(f" {YELLOW}[WARNING] /dev/shm size might be too small, if running in docker increase to at least "
+                    f"--shm-size='1gb'{END}")
+    return size, warn
+
+
+def human_readable_size(size) -> str:
+    units = ["B", "KB", "MB", "GB", "TB", "PB"]
+    i, v = 0, float(size)
+    while v >= 1024 and i < len(units) - 1:
+        v /= 1024
+        i += 1
+    return f"{v:.2f} {units[i]}"
+
+
+def parse_arguments(argv=None):
+    import argparse
+    p = argparse.ArgumentParser(description="environment and native-op report")
+    p.add_argument("--hide_operator_status", action="store_true", help="skip the op compatibility table")
+    p.add_argument("--hide_errors_and_warnings", action="store_true", help="no per-op explanations")
+    return p.parse_args(argv)
+
+
+def main(hide_operator_status: bool = False, hide_errors_and_warnings: bool = False):
+    if not hide_operator_status:
+        op_report(verbose=not hide_errors_and_warnings)
+    rows = debug_report()
+    size, warn = get_shm_size()
+    if size is not None:
+        print(f"{'shared memory (/dev/shm) size':.<30} {human_readable_size(size)}")
+    print(f"{'ninja':.<30} {OKAY if ninja_installed() else NO}")
+    if not hide_errors_and_warnings:
+        for w in warn:
+            print(w)
+    return rows
+
+
+def cli_main(argv=None):
+    args = parse_arguments(argv)
+    main(hide_operator_status=args.hide_operator_status, hide_errors_and_warnings=args.hide_errors_and_warnings)
 
 
 if __name__ == "__main__":

@@ -124,3 +124,35 @@ def shard_chunk_mlp(weight: torch.Tensor, bias, rank: int, world_size: int):
         bg, bu = torch.chunk(bias, 2, dim=0)
         b = torch.cat([bg[start:start + sizes[rank]], bu[start:start + sizes[rank]]], dim=0)
     return w, b
+
+
+def split_by_qkvlist_and_refuse(qkv_list, split_size, split_dim: int = 0, cat_dim: int = 0):
+    """Each of Q, K, V is cut into pieces of ``split_size`` along ``split_dim``; piece ``i`` of all three is joined along
+    ``cat_dim`` - one fused QKV block per tensor-parallel rank (ref: fusedqkv_utils.py:10)."""
+    pieces = [torch.split(m, split_size, dim=split_dim) for m in qkv_list]
+    return [torch.cat([p[i] for p in pieces], dim=cat_dim) for i in range(len(pieces[0]))]
+
+
+def shard_value_with_share_qk(weight: torch.Tensor, bias, rank: int, world_size: int, shard_value: bool = True):
+    """Value (``shard_value``) or output (otherwise) projection of attention blocks whose V heads are shared by pairs of
+    neighbouring Q heads and again by the matching K heads: rank ``r`` owns Q heads ``[r*h, (r+1)*h)`` and needs V head
+    ``q // 2`` for every second one of them, plus the same heads offset by half the head count for the K side. V is cut
+    along its rows, the output projection along its columns (its bias is divided by the world size, to survive the
+    all-reduce); ref: fusedqkv_utils.py:162."""
+    from .tp_shard import get_num_kv_heads
+    dim = 0 if shard_value else 1
+    num_heads = get_num_kv_heads()
+    head_dim = weight.shape[dim] // num_heads
+    assert num_heads % world_size == 0, f"{num_heads} heads do not divide over {world_size} ranks"
+    per_rank = num_heads // world_size
+    first = rank * per_rank
+    v_heads = [(first + i) // 2 for i in range(0, per_rank, 2)]
+    v_heads += [h + num_heads // 2 for h in v_heads]
+    w = torch.cat([weight.narrow(dim, h * head_dim, head_dim) for h in v_heads], dim=dim)
+    if bias is None:
+        return torch.nn.Parameter(w), None
+    if shard_value:
+        b = torch.cat([bias.data[h * head_dim:(h + 1) * head_dim] for h in v_heads], dim=0)
+    else:
+        b = bias.data / float(world_size)
+    return torch.nn.Parameter(w), torch.nn.Parameter(b)

@@ -93,3 +93,59 @@ def revert_transformer_layer(orig_layer_impl, model: torch.nn.Module, config=Non
         else:
             revert_transformer_layer(orig_layer_impl, child, config, preln)
     return model
+
+
+# ---- generic traversal helpers of the reference (replace_module.py:29, 619, 662) ------------------------------------------
+def replace_module(model: torch.nn.Module, orig_class, replace_fn, _replace_policy=None, checkpoint=None) -> torch.nn.Module:
+    """Replace every sub-module of type ``orig_class`` by ``replace_fn(child, _replace_policy, layer_id, prefix=...,
+    state_dict=...)``. With ``orig_class=None`` the registered injection policies decide (their block classes are matched
+    by class name). ``checkpoint`` (``.pt`` / ``.bin`` / ``.safetensors``) is loaded once and handed to ``replace_fn``."""
+    import inspect
+    sd = None
+    if checkpoint is not None:
+        if str(checkpoint).endswith(".safetensors"):
+            from safetensors.torch import load_file
+            sd = load_file(checkpoint)
+        else:
+            sd = torch.load(checkpoint, map_location="cpu", weights_only=False)
+    from .replace_policy import policy_class_names
+    accepts = set(inspect.signature(replace_fn).parameters)
+    counter = {"n": 0}
+
+    def wanted(child) -> bool:
+        if orig_class is not None:
+            return isinstance(child, orig_class) if isinstance(orig_class, type) else type(child).__name__ == str(orig_class)
+        return type(child).__name__ in policy_class_names
+
+    def walk(parent, prefix):
+        for name, child in list(parent.named_children()):
+            full = f"{prefix}.{name}" if prefix else name
+            if wanted(child):
+                kw = {k: v for k, v in (("prefix", full), ("state_dict", sd)) if k in accepts}
+                setattr(parent, name, replace_fn(child, _replace_policy, counter["n"], **kw))
+                counter["n"] += 1
+            else:
+                walk(child, full)
+
+    walk(model, "")
+    return model
+
+
+def get_transformer_name(replaced_module: torch.nn.Module) -> str:
+    """Dotted path of the ModuleList that holds the transformer blocks (``"transformer.h"``, ``"model.layers"``, ...)."""
+    for n, c in replaced_module.named_children():
+        for name, child in c.named_children():
+            if isinstance(child, torch.nn.ModuleList):
+                return f"{n}.{name}"
+    return ""
+
+
+def skip_level_0_prefix(model, state_dict) -> bool:
+    """BLOOM / OPT checkpoints name their tensors without the wrapper's first attribute (``transformer.`` / ``model.``):
+    True when loading must skip that level - unless the keys do start with ``model.``."""
+    import re
+    text = str(model)
+    key = re.search(r": (.*?)Model", text) or re.search(r": (.*?)Stack", text) or re.match(r"(.*?)Model", text)
+    if state_dict is not None and any(re.match(r"^model[.]", k) for k in state_dict.keys()):
+        return False
+    return key is not None and key.group(1).lower() in ("bloom", "opt")

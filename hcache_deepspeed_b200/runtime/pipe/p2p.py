@@ -59,3 +59,8 @@ def recv_obj(src_stage: int, device="cpu"):
     data = torch.empty(int(n[0]), dtype=torch.uint8, device=device)
     recv(data, src_stage)
     return pickle.loads(bytes(data.cpu().numpy().tobytes()))
+
+
+def can_send_recv() -> bool:
+    """Point-to-point ``send`` / ``recv`` (rather than two-rank broadcasts) is available in every torch this runs on."""
+    return hasattr(dist, "send") and hasattr(dist, "recv")

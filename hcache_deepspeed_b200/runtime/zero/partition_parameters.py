@@ -129,7 +129,19 @@ def _convert(param: torch.nn.Parameter, group, remote_device: Optional[str], pin
         _param_swapper.swap_out_and_release([param])       # the slice now lives in its file
 
     def all_gather(param_list: Optional[List] = None, async_op: bool = False, hierarchy: int = 0):
-        all_gather_params(param_list if param_list is not None else [param])
+        """Gather ``param_list`` (default: this parameter). With ``async_op`` the collectives are only launched and a
+        handle is returned whose ``wait()`` completes them."""
+        ps = param_list if param_list is not None else [param]
+        all_gather_params(ps, async_op=async_op)
+        return AllGatherCoalescedHandle(ps) if async_op else None
+
+    def all_gather_coalesced(params, safe_mode: bool = False, quantize: bool = False):
+        """Launch the gathers of ``params`` and return the handle to wait on (ref: partition_parameters.py:1230)."""
+        ps = [q for q in params if q.ds_status == ZeroParamStatus.NOT_AVAILABLE]
+        if not ps:
+            return NoGatherCoalescedHandle(list(params))
+        all_gather_params(ps, async_op=True)
+        return AllGatherCoalescedHandle(list(params))
 
     def partition(param_list: Optional[List] = None, hierarchy: int = 0, has_been_updated: bool = False):
         for p in (param_list if param_list is not None else [param]):
@@ -147,6 +159,7 @@ def _convert(param: torch.nn.Parameter, group, remote_device: Optional[str], pin
                 "persist": param.ds_persist, "device": str(param.device)}
 
     param.all_gather, param.partition, param.partition_numel = all_gather, partition, partition_numel
+    param.all_gather_coalesced = all_gather_coalesced
     param.padding_size, param.ds_summary = padding_size, ds_summary
     if not param.ds_persist:
         _partition_param(param, has_been_updated=False)
@@ -233,6 +246,182 @@ def _wait_inflight(p) -> None:
     p._ds_inflight = None
     p.data = full.narrow(0, 0, p.ds_numel).view(p.ds_shape)
     p.ds_status = ZeroParamStatus.AVAILABLE
+
+
+# ---- handles returned by asynchronous gathers (ref: partition_parameters.py:640-780) --------------------------------------
+class NoGatherHandle:
+    """Nothing is in flight (one rank, or the parameter is already resident)."""
+
+    def __init__(self, param) -> None:
+        if param.ds_status == ZeroParamStatus.INFLIGHT:
+            _wait_inflight(param)
+        self.__param = param
+
+    def wait(self, **kwargs) -> None:
+        self.__param.ds_status = ZeroParamStatus.AVAILABLE
+
+
+class NoGatherCoalescedHandle:
+
+    def __init__(self, params) -> None:
+        self.__params = list(params)
+        self.__complete = False
+
+    def wait(self, **kwargs) -> None:
+        if self.__complete:
+            return
+        for p in self.__params:
+            if p.ds_status == ZeroParamStatus.INFLIGHT:
+                _wait_inflight(p)
+        self.__complete = True
+
+
+class AllGatherHandle:
+    """One parameter's gather: ``wait()`` blocks on the collective and installs the full tensor."""
+
+    def __init__(self, handle, param, quantization=None) -> None:
+        self.__handle, self.__param, self.__quantization = handle, param, quantization
+
+    def wait(self, handle_dependency: bool = True) -> None:
+        if self.__param.ds_status == ZeroParamStatus.INFLIGHT:
+            _wait_inflight(self.__param)
+        elif self.__handle is not None and hasattr(self.__handle, "wait"):
+            self.__handle.wait()
+
+
+class AllGatherCoalescedHandle:
+    """Several parameters gathered together; a second ``wait()`` is an error, as in the reference."""
+
+    def __init__(self, params, allgather_handle=None, partitions=None, world_size: Optional[int] = None, use_secondary_tensor=False,
+                 quantization=None) -> None:
+        self.params = list(params)
+        self.complete = False
+        for p in self.params:
+            if p.ds_status not in (ZeroParamStatus.INFLIGHT, ZeroParamStatus.AVAILABLE):
+                raise RuntimeError(f"expected param {p.ds_summary()} to not be available")
+
+    def wait(self, handle_dependency: bool = True) -> None:
+        if self.complete:
+            return
+        for p in self.params:
+            if p.ds_status == ZeroParamStatus.INFLIGHT:
+                _wait_inflight(p)
+        self.complete = True
+
+
+class MultipleAllGatherHandles:
+
+    def __init__(self, handles) -> None:
+        self.handles = list(handles)
+
+    def wait(self, handle_dependency: bool = True) -> None:
+        for h in self.handles:
+            h.wait(handle_dependency=handle_dependency)
+
+
+class AllReduceCoalescedHandle:
+    """Fetch by all-reduce (``use_all_reduce_for_fetch_params``): every rank contributed its slice in place of a zero
+    buffer; after the reduction each parameter's data is a view of that buffer."""
+
+    def __init__(self, handle, params) -> None:
+        self.handle, self.params, self.complete = handle, list(params), False
+
+    def wait(self, handle_dependency: bool = True) -> None:
+        if self.complete:
+            return
+        if self.handle is not None and hasattr(self.handle, "wait"):
+            self.handle.wait()
+        for p in self.params:
+            if p.ds_status == ZeroParamStatus.INFLIGHT:
+                _wait_inflight(p) if getattr(p, "_ds_inflight", None) is not None else setattr(p, "ds_status", ZeroParamStatus.AVAILABLE)
+        self.complete = True
+
+
+class QuantizationInfo:
+    """What travels next to the int8 codes of a quantised gather (ZeRO++ qwZ)."""
+
+    def __init__(self, quantized_param=None, backend=None, quant_handle=None, scale_buffer=None, partition_sz: int = 0,
+                 world_size: int = 1) -> None:
+        self.quantized_param, self.backend, self.quant_handle = quantized_param, backend, quant_handle
+        self.scale_buffer, self.partition_sz, self.world_size = scale_buffer, partition_sz, world_size
+
+
+class CUDAQuantizer:
+    """Block-wise symmetric int8 quantisation of weight slices for qwZ: groups of ``group_size`` values share a scale
+    (the fused quantisation kernels of ``ops/quantizer`` on the GPU, their torch formulation on the host)."""
+    async_flag = True
+    target_group_size = 8000
+    group_size_cache: dict = {}
+
+    def __init__(self, group_size: int = QWZ_GROUP) -> None:
+        self.group_size = group_size
+
+    def _groups(self, numel: int) -> int:
+        return max(1, -(-numel // self.group_size))
+
+    def quantize(self, param: torch.Tensor, groups: Optional[int] = None):
+        from ...ops.quantizer import quantize_int
+        flat = param.reshape(-1)
+        groups = groups or self._groups(flat.numel())
+        per = -(-flat.numel() // groups)
+        per += per % 2                                        # the packing kernels want an even group length
+        pad = groups * per - flat.numel()
+        if pad:
+            flat = torch.cat([flat, flat.new_zeros(pad)])
+        return quantize_int(flat.float(), groups, 8, symmetric=True)
+
+    def dequantize(self, quantized_param: torch.Tensor, scale: torch.Tensor, dtype: torch.dtype = torch.float32) -> torch.Tensor:
+        from ...ops.quantizer import dequantize_int
+        return dequantize_int(quantized_param, scale, 8, dtype)
+
+
+def free_param(param) -> None:
+    """Drop the full tensor of a parameter nobody uses any more (its partition is untouched)."""
+    assert not getattr(param, "ds_active_sub_modules", None), param.ds_summary() if hasattr(param, "ds_summary") else param
+    param.data = torch.empty(0, dtype=param.dtype, device=getattr(param, "ds_device", param.device))
+    if hasattr(param, "ds_status"):
+        param.ds_status = ZeroParamStatus.NOT_AVAILABLE
+
+
+def get_all_subclasses(cls) -> set:
+    return Init._all_subclasses(cls)
+
+
+def print_rank_0(message, debug: bool = False, force: bool = False) -> None:
+    if (debug or force) and (not dist.is_initialized() or dist.get_rank() == 0):
+        print(message)
+
+
+def debug_rank0(msg: str) -> None:
+    if not dist.is_initialized() or dist.get_rank() == 0:
+        from ...utils.logging import logger
+        logger.debug(msg)
+
+
+def zero_wrapper_for_fp_tensor_constructor(fn, target_fp_dtype: torch.dtype):
+    """``fn`` (``torch.empty`` / ``zeros`` / ``ones`` / ``full`` / ``arange`` / ``eye`` / ``randn``) wrapped so that the
+    floating-point tensors it creates come out in ``target_fp_dtype`` on the current accelerator by default."""
+    import functools
+
+    @functools.wraps(fn)
+    def wrapped(*args, **kwargs):
+        if kwargs.get("device") is None and torch.cuda.is_available():
+            kwargs["device"] = torch.device("cuda", torch.cuda.current_device())
+        t = fn(*args, **kwargs)
+        return t.to(target_fp_dtype) if t.is_floating_point() and "dtype" not in kwargs else t
+
+    return wrapped
+
+
+def get_new_tensor_fn_for_dtype(dtype: torch.dtype):
+    """A ``Tensor.new_tensor`` replacement whose floating-point results are ``dtype``."""
+
+    def new_tensor(cls, *args, **kwargs):
+        t = torch.Tensor.new_empty(cls, []).new_tensor(*args, **kwargs) if not isinstance(cls, torch.Tensor) else \
+            torch.Tensor.new_tensor(cls, *args, **kwargs)
+        return t.to(dtype) if t.is_floating_point() else t
+
+    return new_tensor
 
 
 class Init:
@@ -456,3 +645,7 @@ def shutdown_init_context():
 
 def restore_init_context():
     pass
+
+
+# the reference splits Init into a generic "patch every nn.Module subclass" base and the ZeRO part; here it is one class
+InsertPostInitMethodToModuleSubClasses = Init

@@ -134,3 +134,34 @@ class DistributedAttention(torch.nn.Module):
         v = _SeqAllToAll.apply(self.spg, value, self.scatter_idx, self.gather_idx, batch_dim_idx)
         ctx = self.local_attn(q, k, v, *args, **kwargs)
         return _SeqAllToAll.apply(self.spg, ctx, self.gather_idx, self.scatter_idx, batch_dim_idx, query.shape[2])
+
+
+# ---- small helpers the reference exports from this module (sequence/layer.py:59-108) ---------------------------------------
+def pre_all2all_fun(permute_idx, inp_shape, input: Tensor) -> Tensor:
+    """View ``input`` as ``inp_shape`` and (optionally) permute it into the layout the all-to-all sends."""
+    x = input.reshape(inp_shape).contiguous()
+    return x.permute(permute_idx).contiguous() if permute_idx is not None else x
+
+
+def post_all2all(permute_idx, res_shape):
+    """The matching receive-side step: returns a function that permutes (optionally) and reshapes to ``res_shape``."""
+
+    def post_func(input: Tensor) -> Tensor:
+        x = input.permute(permute_idx).contiguous() if permute_idx is not None else input
+        return x.reshape(res_shape).contiguous()
+
+    return post_func
+
+
+def _rotate_half(x: Tensor) -> Tensor:
+    x1, x2 = x.reshape(*x.shape[:-1], 2, x.shape[-1] // 2).unbind(dim=-2)
+    return torch.cat((-x2, x1), dim=-1)
+
+
+def apply_rotary_pos_emb(t: Tensor, freqs_cos: Tensor, freqs_sin: Tensor) -> Tensor:
+    """Half-split rotary embedding on ``t`` of shape ``[seq, ..., dim]`` with per-position ``cos`` / ``sin`` tables of
+    shape ``[seq, ..., rot_dim]``; features beyond ``rot_dim`` pass through."""
+    rot = freqs_cos.shape[-1]
+    head, rest = t[..., :rot], t[..., rot:]
+    head = head * freqs_cos + _rotate_half(head) * freqs_sin
+    return head if rest.shape[-1] == 0 else torch.cat((head, rest), dim=-1)

@@ -65,3 +65,25 @@ def log_rank_file(rank, *msgs):
     with open(f"log_rank_{rank}.txt", "a") as fh:
         for m in msgs:
             fh.write(f"{m}\n")
+
+
+def print_backward_tensors(tensor) -> None:
+    """Walk the autograd graph below ``tensor`` and print every leaf variable it reaches (id, shape, value, grad)."""
+    seen = set()
+
+    def walk(fn):
+        if fn is None or id(fn) in seen:
+            return
+        seen.add(id(fn))
+        print(f"Backward tensors in {fn}")
+        for nxt, _ in fn.next_functions:
+            if nxt is None:
+                continue
+            var = getattr(nxt, "variable", None)
+            if var is not None:
+                print(nxt)
+                print(f"Tensor - id: {id(var)}, shape: {var.shape}, data: {var}, grad: {var.grad}")
+            else:
+                walk(nxt)
+
+    walk(getattr(tensor, "grad_fn", None))

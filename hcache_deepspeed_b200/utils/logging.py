@@ -90,3 +90,10 @@ def should_log_le(max_log_level_str: str) -> bool:
     if key not in _LOG_LEVELS:
         raise ValueError(f"{max_log_level_str} is not one of the logging levels")
     return get_current_level() <= _LOG_LEVELS[key]
+
+
+def print_configuration(args, name: str) -> None:
+    """Log every attribute of an argparse namespace / config object, one dotted line each."""
+    logger.info(f"{name}:")
+    for arg in sorted(vars(args)):
+        logger.info(f"  {arg} {'.' * max(1, 29 - len(arg))} {getattr(args, arg)}")

@@ -71,3 +71,35 @@ def bind_to_gpu_numa(gpu_index: int) -> List[int]:
         return cpus
     except Exception:
         return []
+
+
+def parse_range(rng: str) -> range:
+    """``"5"`` -> range(5, 6); ``"2-4"`` -> range(2, 5)."""
+    try:
+        v = int(rng)
+        return range(v, v + 1)
+    except ValueError:
+        parts = rng.split("-")
+        if len(parts) != 2:
+            raise ValueError(f"Bad range: '{rng}', range must be either a number or two number separated by dash")
+        lo, hi = int(parts[0]), int(parts[1])
+        if lo > hi:
+            raise ValueError(f"Bad range: '{rng}', range end must larger than or equal to start")
+        return range(lo, hi + 1)
+
+
+def check_for_numactl_pkg() -> bool:
+    """Is the ``numactl`` tool usable here (the launcher's ``--bind_cores_to_rank`` needs it)? The binary on PATH is what
+    counts; when it is missing the distribution's package manager is asked so the message can name the install command."""
+    import shutil
+    import subprocess
+    if shutil.which("numactl") is not None:
+        return True
+    for mgr, (flag, tool) in {"dpkg": ("-l", "apt"), "pacman": ("-Q", "pacman"), "rpm": ("-q", "yum")}.items():
+        if shutil.which(mgr) is None:
+            continue
+        ok = subprocess.run([mgr, flag, "numactl"], stdout=subprocess.DEVNULL, stderr=subprocess.DEVNULL).returncode == 0
+        if not ok:
+            print(f"please install the numactl package with {tool}")
+        return ok
+    return False

@@ -250,3 +250,15 @@ class ThroughputTimer:
         if self.global_step_count > self.start_step and self.total_elapsed_time > 0:
             return self.batch_size / (self.total_elapsed_time / (self.global_step_count - self.start_step))
         return float("-inf")
+
+
+def trim_mean(data, trim_percent: float) -> float:
+    """Mean after dropping the ``trim_percent`` smallest and largest share of ``data`` (0 for an empty list)."""
+    assert 0.0 <= trim_percent <= 1.0
+    n = len(data)
+    if n == 0:
+        return 0
+    ordered = sorted(data)
+    k = int(round(n * trim_percent))
+    kept = ordered[k:n - k] or ordered
+    return sum(kept) / len(kept)

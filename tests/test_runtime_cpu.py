@@ -764,3 +764,39 @@ def test_partitioned_tensor_and_group_names_2ranks():
         assert r["gathered"] == [1.0] * 4 + [2.0] * 4 and r["gathered_sharded"] == [0.0, 1.0, 2.0, 3.0, 10.0, 11.0, 12.0, 13.0], r
         assert r["mpu"] == (1, 0, 2, rank, rank) and r["mpu_pinned"] == (2, rank, 0) and r["obj"] == {"a": 0}, r
     assert res[0]["uneven"][2] + res[1]["uneven"][2] == 15
+
+
+def test_zero3_async_gather_handles_and_quantizer():
+    """``param.all_gather(async_op=True)`` / ``all_gather_coalesced`` hand back handles to wait on; ``free_param``;
+    the qwZ quantiser round trip (ref: partition_parameters.py:640-780, 1230)."""
+    import hcache_deepspeed_b200 as ds
+    from hcache_deepspeed_b200.runtime.zero import ZeroParamStatus
+    from hcache_deepspeed_b200.runtime.zero import partition_parameters as PP
+    torch.manual_seed(0)
+    model = torch.nn.Sequential(torch.nn.Linear(8, 16), torch.nn.Linear(16, 2))
+    want = [p.detach().clone() for p in model.parameters()]
+    ds.initialize(model=model, config={"train_micro_batch_size_per_gpu": 1, "optimizer": {"type": "SGD", "params": {"lr": 0.1}},
+                                       "zero_optimization": {"stage": 3, "stage3_param_persistence_threshold": 0}, "steps_per_print": 1000})
+    ps = list(model.parameters())
+    assert all(p.ds_status == ZeroParamStatus.NOT_AVAILABLE for p in ps)
+    h = ps[0].all_gather_coalesced(ps[:2])
+    assert isinstance(h, PP.AllGatherCoalescedHandle)
+    h.wait()
+    h.wait()
+    assert all(p.ds_status == ZeroParamStatus.AVAILABLE and torch.equal(p.data, w) for p, w in zip(ps[:2], want[:2]))
+    assert isinstance(ps[0].all_gather_coalesced(ps[:2]), PP.NoGatherCoalescedHandle)
+    h2 = ps[2].all_gather(async_op=True)
+    PP.MultipleAllGatherHandles([h2, PP.NoGatherHandle(ps[0])]).wait()
+    assert ps[2].ds_status == ZeroParamStatus.AVAILABLE and torch.equal(ps[2].data, want[2])
+    PP.free_param(ps[2])
+    assert ps[2].ds_status == ZeroParamStatus.NOT_AVAILABLE and ps[2].numel() == 0
+    ps[2].all_gather()
+    assert torch.equal(ps[2].data, want[2])
+    q = PP.CUDAQuantizer(group_size=64)
+    x = torch.randn(1000)
+    codes, scale = q.quantize(x)
+    back = q.dequantize(codes, scale).reshape(-1)[:1000]
+    assert codes.dtype == torch.int8 and float((back - x).abs().max()) < float(x.abs().max()) / 100
+    assert torch.nn.Linear in PP.get_all_subclasses(torch.nn.Module) and PP.InsertPostInitMethodToModuleSubClasses is PP.Init
+    f = PP.zero_wrapper_for_fp_tensor_constructor(torch.ones, torch.bfloat16)
+    assert f(3).dtype == torch.bfloat16 and f(3, dtype=torch.int32).dtype == torch.int32
