@@ -18,6 +18,24 @@ import types
 PACKAGE = __name__.rsplit(".", 1)[0]
 
 ALIASES = {
+    # v2 module configs / interfaces: one file each here, a package of small files in the reference
+    "inference.v2.modules.configs.attention_configs": [("inference.v2.modules.configs", n, n) for n in ("PositionalEmbeddingType", "RotateHalfConfig", "MaskingType", "DSSelfAttentionConfig")],
+    "inference.v2.modules.configs.embedding_config": [("inference.v2.modules.configs", "DSEmbeddingsConfig", "DSEmbeddingsConfig")],
+    "inference.v2.modules.configs.linear_config": [("inference.v2.modules.configs", "DSLinearConfig", "DSLinearConfig")],
+    "inference.v2.modules.configs.moe_config": [("inference.v2.modules.configs", "DSMoEConfig", "DSMoEConfig")],
+    "inference.v2.modules.configs.norm_config": [("inference.v2.modules.configs", "DSNormConfig", "DSNormConfig"), ("inference.v2.modules.configs", "NormTypeEnum", "NormTypeEnum")],
+    "inference.v2.modules.configs.unembed_config": [("inference.v2.modules.configs", "DSUnembedConfig", "DSUnembedConfig")],
+    "inference.v2.modules.interfaces.attention_base": [("inference.v2.modules.interfaces", n, n) for n in ("DSSelfAttentionBase", "DSSelfAttentionRegistry")],
+    "inference.v2.modules.interfaces.embedding_base": [("inference.v2.modules.interfaces", n, n) for n in ("DSEmbeddingBase", "DSEmbeddingRegistry")],
+    "inference.v2.modules.interfaces.linear_base": [("inference.v2.modules.interfaces", n, n) for n in ("DSLinearBase", "DSLinearRegistry")],
+    "inference.v2.modules.interfaces.moe_base": [("inference.v2.modules.interfaces", n, n) for n in ("DSMoEBase", "DSMoERegistry")],
+    "inference.v2.modules.interfaces.post_norm_base": [("inference.v2.modules.interfaces", n, n) for n in ("DSPostNormBase", "DSPostNormRegistry")],
+    "inference.v2.modules.interfaces.pre_norm_base": [("inference.v2.modules.interfaces", n, n) for n in ("DSPreNormBase", "DSPreNormRegistry")],
+    "inference.v2.modules.interfaces.unembed_base": [("inference.v2.modules.interfaces", n, n) for n in ("DSUnembedBase", "DSUnembedRegistry")],
+    # the tuners live in autotuning/tuner.py
+    "autotuning.tuner.base_tuner": [("autotuning.tuner", "BaseTuner", "BaseTuner")],
+    "autotuning.tuner.index_based_tuner": [("autotuning.tuner", "RandomTuner", "RandomTuner"), ("autotuning.tuner", "GridSearchTuner", "GridSearchTuner")],
+    "autotuning.tuner.model_based_tuner": [("autotuning.tuner", "ModelBasedTuner", "ModelBasedTuner")],
     # one v1 fused-layer class covers what the reference splits into per-family subclasses
     "model_implementations.transformers.ds_base": [("model_implementations.transformers.ds_transformer", "DeepSpeedTransformerInference", "DeepSpeedTransformerBase")],
     "model_implementations.transformers.ds_bert": [("model_implementations.transformers.ds_transformer", "DeepSpeedTransformerInference", "DeepSpeedBERTInference")],
@@ -39,7 +57,6 @@ ALIASES = {
     "checkpoint.reshape_utils": [("checkpoint.reshape", "*", "*"), ("checkpoint.reshape", "meg_2d_parallel_map", "meg_2d_parallel_map"), ("checkpoint.reshape", "model_3d_desc", "model_3d_desc"), ("checkpoint.reshape", "ZeROCheckpoint", "ZeROCheckpoint")],
     "checkpoint.utils": [("checkpoint.reshape", "*", "*"), ("checkpoint.reshape", "meg_2d_parallel_map", "meg_2d_parallel_map"), ("checkpoint.reshape", "model_3d_desc", "model_3d_desc"), ("checkpoint.reshape", "ZeROCheckpoint", "ZeROCheckpoint")],
     "checkpoint.zero_checkpoint": [("checkpoint.reshape", "*", "*"), ("checkpoint.reshape", "meg_2d_parallel_map", "meg_2d_parallel_map"), ("checkpoint.reshape", "model_3d_desc", "model_3d_desc"), ("checkpoint.reshape", "ZeROCheckpoint", "ZeROCheckpoint")],
-    "compression.config": [("compression.compress", "get_compression_config", "get_compression_config")],
     "elasticity.config": [("elasticity.elasticity", "ElasticityConfig", "ElasticityConfig"), ("elasticity.elasticity", "ElasticityConfigError", "ElasticityConfigError"), ("elasticity.elasticity", "ElasticityError", "ElasticityError"), ("elasticity.elasticity", "ElasticityIncompatibleWorldSize", "ElasticityIncompatibleWorldSize")],
     "inference.v2.model_implementations.inference_transformer_base": [("inference.v2.model_implementations.inference_model_base", "DSInferenceModelBase", "DSInferenceModelBase"), ("inference.v2.model_implementations.inference_model_base", "DSTransformerModelBase", "DSTransformerModelBase")],
     "inference.v2.modules.module_registry": [("inference.v2.modules.ds_module", "ConfigBundle", "ConfigBundle"), ("inference.v2.modules.ds_module", "DSModuleRegistryBase", "DSModuleRegistryBase")],

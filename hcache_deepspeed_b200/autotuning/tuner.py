@@ -120,3 +120,7 @@ class ModelBasedTuner(BaseTuner):
                 i = int(np.argmin(preds) if self.metric == "latency" else np.argmax(preds))
             batch.append(self.all_exps.pop(i))
         return batch
+
+
+# `autotuning.tuner` is a package in the reference; its sub-module paths import through this module (see _import_paths.py)
+__path__: list = []

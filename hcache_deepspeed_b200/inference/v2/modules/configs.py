@@ -94,3 +94,8 @@ class DSUnembedConfig(_TorchCfg):
     vocab_size: int
     max_sequences: int = 64
     model_dim: int = 0
+
+
+# the reference has this as a package of small files; `__path__` lets its sub-module paths (served from the alias table in
+# _import_paths.py) import through this module
+__path__: list = []

@@ -5,3 +5,8 @@ from .implementations import (DSAttentionRegistry, DSEmbeddingBase, DSEmbeddingR
                               DSSelfAttentionBase, DSUnembedBase, DSUnembedRegistry)
 
 DSSelfAttentionRegistry = DSAttentionRegistry
+
+
+# the reference has this as a package of small files; `__path__` lets its sub-module paths (served from the alias table in
+# _import_paths.py) import through this module
+__path__: list = []

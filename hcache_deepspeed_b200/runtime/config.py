@@ -420,3 +420,8 @@ class DeepSpeedConfig:
     def print_user_config(self):
         from ..utils.logging import logger
         logger.info("  json = " + json.dumps(self._param_dict, sort_keys=True, indent=4, default=str))
+
+
+# single-entry readers of a raw config dict under the reference's names (used by integrations that hold only the JSON)
+from .config_getters import *  # noqa: E402,F401,F403
+from .config_getters import DeepSpeedConfigWriter, DtypeEnum, HybridEngineConfig, ValidationMode, get_scalar_param  # noqa: E402,F401

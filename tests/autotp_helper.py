@@ -245,3 +245,68 @@ def tp_training_worker(rank, world, tp):
         got.append(float(loss.detach()))
     return {"want": [w[rank // tp] for w in want], "got": got, "dp": engine.dp_world_size,
             "q_rows": model.model.layers[0].self_attn.q_proj.weight.shape[0]}
+
+
+def tp_layers_worker(rank, world):
+    """The layers that shard themselves from a full module (``Layer(module, mp_group)``; ref: module_inject/layers.py:142-720):
+    column / row parallel linears, their Conv1D variants, packed gate-up, sharded Conv2d; frozen in inference mode, trainable
+    with complete gradients in training mode, and reassembled by ``gather_params``."""
+    import copy
+    import torch
+    import hcache_deepspeed_b200 as ds
+    from hcache_deepspeed_b200.module_inject import layers as L
+    from transformers.pytorch_utils import Conv1D
+    ds.init_distributed(dist_backend="gloo")
+    group = ds.comm.new_group(list(range(world)))
+    torch.manual_seed(0)
+    out = {}
+    x = torch.randn(2, 5, 6)
+    up, down = torch.nn.Linear(6, 6), torch.nn.Linear(6, 4)
+    want = down(torch.relu(up(x)))
+    col = L.LinearLayer(copy.deepcopy(up), mp_group=group)
+    row = L.LinearAllreduce(copy.deepcopy(down), group)
+    col.eval(), row.eval()
+    got = row(torch.relu(col(x)))
+    out["col_err"] = float((col(x) - up(x).chunk(world, dim=-1)[rank]).abs().max())
+    out["row_err"] = float((got - want).abs().max())
+    out["col_shape"], out["row_shape"] = tuple(col.weight.shape), tuple(row.weight.shape)
+    out["frozen"] = not col.weight.requires_grad and not row.weight.requires_grad and col.weight.tensor_model_parallel
+    # Conv1D-born variants
+    c_up, c_down = Conv1D(6, 6), Conv1D(4, 6)
+    torch.nn.init.normal_(c_up.weight), torch.nn.init.normal_(c_down.weight)
+    want_c = c_down(torch.relu(c_up(x)))
+    ccol = L.conv_LinearLayer(copy.deepcopy(c_up), mp_group=group).eval()
+    crow = L.Conv_LinearALlreduce(copy.deepcopy(c_down), group).eval()
+    out["conv_err"] = float((ccol(x) - c_up(x).chunk(world, dim=-1)[rank]).abs().max())
+    out["convrow_err"] = float((crow(torch.relu(ccol(x))) - want_c).abs().max())
+    # packed gate+up: every rank holds matching slices of both halves
+    packed = torch.nn.Linear(6, 8)
+    gu = L.GateUpPack_LinearLayer(copy.deepcopy(packed), mp_group=group).eval()
+    g_full, u_full = packed(x).chunk(2, dim=-1)
+    g, u = gu(x).chunk(2, dim=-1)
+    out["gateup_err"] = float(max((g - g_full.chunk(world, dim=-1)[rank]).abs().max(), (u - u_full.chunk(world, dim=-1)[rank]).abs().max()))
+    # Conv2d sharded over output channels, then over input channels with a reduced sum
+    conv_a, conv_b = torch.nn.Conv2d(3, 4, 3, padding=1), torch.nn.Conv2d(4, 2, 1)
+    img = torch.randn(1, 3, 5, 5)
+    want_img = conv_b(conv_a(img))
+    oc = L.TensorParallelOcShardConv2d(copy.deepcopy(conv_a), rank, world)
+    ic = L.TensorParallelIcShardConv2d(copy.deepcopy(conv_b), rank, world)
+    out["conv2d_err"] = float((ic(oc(img)) - want_img).abs().max())
+    # training mode: shards get gradients, the input gradient is complete, gather_params rebuilds the full weight
+    L.set_autotp_mode(training=True)
+    out["mode_roundtrip"] = L.is_autotp_training_mode()
+    tcol = L.LinearLayer(copy.deepcopy(up), mp_group=group).train()
+    trow = L.LinearAllreduce(copy.deepcopy(down), group).train()
+    out["trainable"] = tcol.weight.requires_grad and trow.weight.requires_grad
+    xi = x.clone().requires_grad_(True)
+    trow(torch.relu(tcol(xi))).pow(2).sum().backward()
+    xr = x.clone().requires_grad_(True)
+    down(torch.relu(up(xr))).pow(2).sum().backward()
+    out["train_grad_err"] = float(max((xi.grad - xr.grad).abs().max(),
+                                      (tcol.weight.grad - up.weight.grad.chunk(world, dim=0)[rank]).abs().max()))
+    tcol.gather_params([tcol.weight, tcol.bias])
+    trow.gather_params([trow.weight])
+    out["gathered"] = bool(torch.equal(tcol.weight.data, up.weight.data) and torch.equal(trow.weight.data, down.weight.data))
+    L.set_autotp_mode(training=False)
+    out["mode_roundtrip"] = out["mode_roundtrip"] and not L.is_autotp_training_mode()
+    return out

@@ -110,3 +110,13 @@ def test_training_tensor_parallelism_matches_unsharded_model(world, tp):
     for r in run_distributed(tp_training_worker, world, tp, timeout=600):
         assert r["dp"] == world // tp and r["q_rows"] == 64 // tp
         assert r["got"] == pytest.approx(r["want"], rel=2e-4, abs=2e-4), r
+
+
+def test_self_partitioning_tp_layers_2ranks():
+    from tests.autotp_helper import tp_layers_worker
+    from tests.dist_utils import run_distributed
+    for r in run_distributed(tp_layers_worker, 2):
+        assert r["col_err"] < 1e-5 and r["row_err"] < 1e-5 and r["conv_err"] < 1e-5 and r["convrow_err"] < 1e-5, r
+        assert r["col_shape"] == (3, 6) and r["row_shape"] == (4, 3) and r["frozen"], r
+        assert r["gathered"] and r["train_grad_err"] < 1e-5 and r["trainable"], r
+        assert r["conv2d_err"] < 1e-5 and r["gateup_err"] < 1e-5 and r["mode_roundtrip"], r
