@@ -764,3 +764,61 @@ def unwrap_model_for_generation(model):
             if offload is not None:
                 offload._install(offload.module)
                 offload.reset_trace()
+
+
+# ---- printed estimate tables (ref: stage3.py:3044-3150) ----------------------------------------------------------------------
+def model_to_params(model: torch.nn.Module):
+    """(parameter count with tied parameters once, parameter count of the largest single module)."""
+    total = sum({p.data_ptr(): p.numel() for p in model.parameters()}.values())
+    largest = max((sum(p.numel() for p in m.parameters(recurse=False)) for m in model.modules()), default=0)
+    return total, largest
+
+
+def estimate_zero3_model_states_mem_needs_all_cold(total_params: int, largest_layer_params: int, num_gpus_per_node: int = 1,
+                                                   num_nodes: int = 1, additional_buffer_factor: float = 1.5):
+    """Print the per-CPU / per-GPU memory for params + optimizer states + gradients under ZeRO-3 for every combination of
+    optimizer offload, parameter offload and ``zero.Init``; returns the rows."""
+    print("Estimated memory needed for params, optim states and gradients for a:\n"
+          f"HW: Setup with {num_nodes} {'nodes' if num_nodes > 1 else 'node'}, {num_gpus_per_node} "
+          f"{'GPUs' if num_gpus_per_node > 1 else 'GPU'} per node.\n"
+          f"SW: Model with {int(total_params / 1e6)}M total params, {int(largest_layer_params / 1e6)}M largest layer params.")
+    print("  per CPU  |  per GPU |   Options")
+    rows = []
+    for cpu_offload in (True, False):
+        for cpu_offload_params in (True, False):
+            if cpu_offload_params and not cpu_offload:
+                continue
+            for zero_init in (True, False):
+                cpu_mem, gpu_mem, _ = estimate_zero3_model_states_mem_needs(
+                    total_params=total_params, largest_layer_params=largest_layer_params, num_gpus_per_node=num_gpus_per_node,
+                    num_nodes=num_nodes, cpu_offload=cpu_offload, cpu_offload_params=cpu_offload_params, zero_init=zero_init,
+                    additional_buffer_factor=additional_buffer_factor)
+                opts = (f"offload_param={'cpu ' if cpu_offload_params else 'none'}, offload_optimizer="
+                        f"{'cpu ' if cpu_offload else 'none'}, zero_init={1 if zero_init else 0}")
+                print(f" {cpu_mem / 2**30:7.2f}GB | {gpu_mem / 2**30:6.2f}GB | {opts}")
+                rows.append((cpu_mem, gpu_mem, opts))
+    return rows
+
+
+def estimate_zero3_model_states_mem_needs_all_live(model: torch.nn.Module, num_gpus_per_node: int = 1, num_nodes: int = 1,
+                                                   additional_buffer_factor: float = 1.5):
+    total, largest = model_to_params(model)
+    return estimate_zero3_model_states_mem_needs_all_cold(total, largest, num_gpus_per_node, num_nodes, additional_buffer_factor)
+
+
+def move_to_cpu(tensor_list) -> None:
+    for t in tensor_list:
+        t.data = t.data.cpu()
+
+
+def lcm(x: int, y: int) -> int:
+    return x * y // math.gcd(x, y)
+
+
+def isclose(a, b, rtol: float = 1e-09, atol: float = 0.0) -> bool:
+    return abs(a - b) <= max(rtol * max(abs(a), abs(b)), atol)
+
+
+def print_rank_0(message, debug: bool = False, force: bool = False) -> None:
+    if (debug or force) and (not dist.is_initialized() or dist.get_rank() == 0):
+        logger.info(message)

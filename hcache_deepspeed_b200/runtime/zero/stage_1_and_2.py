@@ -460,3 +460,64 @@ def estimate_zero2_model_states_mem_needs(total_params: int, num_gpus_per_node: 
         gpu_mem = 4 * total_params + int(16 * total_params / total_gpus)
         cpu_mem = total_params * 4 * num_gpus_per_node * additional_buffer_factor
     return int(cpu_mem), int(gpu_mem)
+
+
+# ---- printed estimate tables (ref: stage_1_and_2.py:2462-2540) ------------------------------------------------------------
+def model_to_params(model: torch.nn.Module) -> int:
+    """Parameter count with tied parameters counted once."""
+    return sum({p.data_ptr(): p.numel() for p in model.parameters()}.values())
+
+
+def _hw_line(num_nodes: int, num_gpus_per_node: int) -> str:
+    return (f"HW: Setup with {num_nodes} {'nodes' if num_nodes > 1 else 'node'}, {num_gpus_per_node} "
+            f"{'GPUs' if num_gpus_per_node > 1 else 'GPU'} per node.")
+
+
+def estimate_zero2_model_states_mem_needs_all_cold(total_params: int, num_gpus_per_node: int = 1, num_nodes: int = 1,
+                                                   additional_buffer_factor: float = 1.5):
+    """Print the per-CPU / per-GPU memory for params + optimizer states + gradients under ZeRO-2, with and without
+    optimizer offload, for a model given only by its parameter count; returns the rows."""
+    print("Estimated memory needed for params, optim states and gradients for a:\n"
+          f"{_hw_line(num_nodes, num_gpus_per_node)}\nSW: Model with {int(total_params / 1e6)}M total params.")
+    print("  per CPU  |  per GPU |   Options")
+    rows = []
+    for cpu_offload in (True, False):
+        cpu_mem, gpu_mem = estimate_zero2_model_states_mem_needs(total_params=total_params, num_gpus_per_node=num_gpus_per_node,
+                                                                 num_nodes=num_nodes, cpu_offload=cpu_offload,
+                                                                 additional_buffer_factor=additional_buffer_factor)
+        opts = f"offload_optimizer={'cpu ' if cpu_offload else 'none'}"
+        print(f" {cpu_mem / 2**30:7.2f}GB | {gpu_mem / 2**30:6.2f}GB | {opts}")
+        rows.append((cpu_mem, gpu_mem, opts))
+    return rows
+
+
+def estimate_zero2_model_states_mem_needs_all_live(model: torch.nn.Module, num_gpus_per_node: int = 1, num_nodes: int = 1,
+                                                   additional_buffer_factor: float = 1.5):
+    return estimate_zero2_model_states_mem_needs_all_cold(model_to_params(model), num_gpus_per_node, num_nodes,
+                                                          additional_buffer_factor)
+
+
+def get_alignment_padding(tensor_list, alignment: int) -> int:
+    """Elements to append so that the total of ``tensor_list`` is a multiple of ``alignment``."""
+    rem = sum(t.numel() for t in tensor_list) % alignment
+    return (alignment - rem) if rem else 0
+
+
+def lcm(x: int, y: int) -> int:
+    return x * y // math.gcd(x, y)
+
+
+def isclose(a, b, rtol: float = 1e-09, atol: float = 0.0) -> bool:
+    return abs(a - b) <= max(rtol * max(abs(a), abs(b)), atol)
+
+
+def split_half_float_double(tensors):
+    """Group tensors by (device kind, dtype): one bucket per combination present, in a fixed dtype order."""
+    order = (torch.float16, torch.float32, torch.float64, torch.bfloat16)
+    kind = tensors[0].device.type if tensors else "cpu"
+    return [[t for t in tensors if t.dtype == dt and t.device.type == kind] for dt in order
+            if any(t.dtype == dt and t.device.type == kind for t in tensors)]
+
+
+def print_rank_msg(msg) -> None:
+    print(f"rank {dist.get_rank() if dist.is_initialized() else 0} - {msg}")

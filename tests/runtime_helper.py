@@ -241,6 +241,16 @@ def ckpt_tools_worker(rank, world, stage, save_dir, mode):
         return {k: v.detach().float().clone() for k, v in engine.module.state_dict().items()}
     from hcache_deepspeed_b200.checkpoint import load_universal_into_engine
     n = load_universal_into_engine(engine, save_dir)
+    if stage == 3:
+        from hcache_deepspeed_b200.runtime.zero import GatheredParameters
+        state = {}
+        for name, p in engine.module.named_parameters():
+            with GatheredParameters([p]):
+                state[name] = p.data.detach().float().clone()
+        m = engine.optimizer.fp32_partitioned_groups_flat[0]
+        sq = torch.tensor([float(engine.optimizer.optimizer.state[m]["exp_avg"].norm()) ** 2])
+        ds.comm.all_reduce(sq)
+        return {"restored": n, "state": state, "exp_avg_norm": float(sq.sqrt())}
     out = {"restored": n, "state": {k: v.detach().float().clone() for k, v in engine.module.state_dict().items()}}
     m = engine.optimizer.single_partition_of_fp32_groups[0]
     out["exp_avg_norm"] = float(engine.optimizer.optimizer.state[m]["exp_avg"].norm())

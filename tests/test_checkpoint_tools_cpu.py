@@ -171,3 +171,65 @@ def test_deepspeed_checkpoint_2d_views_of_a_pipeline_checkpoint(tmp_path):
     assert [os.path.basename(f) for f in one.get_2d_parallel_files(0, 0)] == [f"mp_rank_{r:02d}_model_states.pt" for r in range(4)]
     assert one.get_2d_parallel_state(0, 0)["iteration"] == 17
     one.show_2d_mapping(); one.show_tp_embedding_map(); one.show_tp_final_norm_map(); one.show_pp_transformer_map(); one.show_transformer_file_map()
+
+
+def test_universal_checkpoint_from_and_into_zero3(tmp_path):
+    """ZeRO-3 (dp 2) -> universal -> ZeRO-3 under dp 3 and ZeRO-1 under dp 1: weights and Adam moments survive
+    (ref: ds_to_universal.py extract_zero_shards_stage3 / merge_zero3_slices, stage3.py load_hp_checkpoint_state)."""
+    from hcache_deepspeed_b200.checkpoint import convert_to_universal
+    d = str(tmp_path / "ck")
+    states = run_distributed(ckpt_tools_worker, 2, 3, d, "save")
+    uni = convert_to_universal(d, str(tmp_path / "ck" / "t3_universal"), tag="t3")
+    norms = []
+    for world, stage in ((3, 3), (1, 1)):
+        res = run_distributed(ckpt_tools_worker, world, stage, uni, "universal")
+        for r in res:
+            assert r["restored"] == len(states[0]) and r["exp_avg_norm"] > 0
+            for k, v in states[0].items():
+                torch.testing.assert_close(r["state"][k], v, rtol=1e-6, atol=1e-7)
+        norms.append(res[0]["exp_avg_norm"])
+    assert norms[0] == pytest.approx(norms[1], rel=1e-5)       # the same moments, whatever layout they were cut into
+
+
+def test_universal_tp_merge_rules_and_reslicing(tmp_path):
+    """Joining tensor-parallel slices by the checkpoint's pattern lists, and cutting them again for another tp degree
+    (ref: ds_to_universal.py merge_tp_slices :232, universal_checkpoint.py load_hp_checkpoint_state)."""
+    from hcache_deepspeed_b200.checkpoint.ds_to_universal import dump_param_fragment, merge_tp_slices
+    from hcache_deepspeed_b200.checkpoint.universal_checkpoint import SubparamShape, load_hp_checkpoint_state
+    info = {"tp_replicated_parameter_patterns": [r".*norm.weight"], "parameter_to_average_patterns": [r".*router.bias"],
+            "parameter_with_row_parallelism_patterns": [r".*dense.weight"], "vocabulary_parameter_patterns": [r".*embed.weight"],
+            "parameter_with_2_sub_params_cat_dim_0": [r".*gate_up.weight"], "original_vocab_size": 10,
+            "parameter_with_sub_params": [dict(patterns=[r".*qkv.weight"], shape=((8, 4, 4), 6), partition_dim=0)]}
+    g = torch.Generator().manual_seed(0)
+    full = {"l.norm.weight": torch.randn(6, generator=g), "l.router.bias": torch.randn(4, generator=g),
+            "l.dense.weight": torch.randn(6, 8, generator=g), "l.col.weight": torch.randn(8, 6, generator=g),
+            "l.gate_up.weight": torch.randn(16, 6, generator=g), "l.qkv.weight": torch.randn(16, 6, generator=g),
+            "l.embed.weight": torch.randn(10, 6, generator=g)}
+
+    def cut(name, t, r, tp=2):
+        if "norm" in name:
+            return t.clone()
+        if "router" in name:
+            return t + (0.5 if r == 0 else -0.5)
+        if "dense" in name:
+            return t.chunk(tp, dim=1)[r]
+        if "gate_up" in name:
+            return torch.cat([h.chunk(tp, dim=0)[r] for h in t.chunk(2, dim=0)], dim=0)
+        if "qkv" in name:
+            return torch.cat([p.chunk(tp, dim=0)[r] for p in t.split([8, 4, 4], dim=0)], dim=0)
+        if "embed" in name:
+            return torch.cat([t, torch.zeros(2, 6)], dim=0).chunk(tp, dim=0)[r]      # vocabulary padded to 12 rows
+        return t.chunk(tp, dim=0)[r]
+
+    for name, t in full.items():
+        merged, meta = merge_tp_slices(name, [cut(name, t, r) for r in range(2)], info)
+        torch.testing.assert_close(merged, t)
+        dump_param_fragment(str(tmp_path / "zero"), name, {"fp32": merged}, meta)
+        for tp in (1, 2):
+            for r in range(tp):
+                got = load_hp_checkpoint_state(str(tmp_path), name, "fp32", tp_rank=r, tp_world_size=tp, padded_vocab_size=12)
+                want = cut(name, t, r, tp) if tp > 1 else (torch.cat([t, torch.zeros(2, 6)]) if "embed" in name else t)
+                if "router" in name:
+                    want = t
+                torch.testing.assert_close(got, want)
+    assert isinstance(SubparamShape(**info["parameter_with_sub_params"][0]).shape, tuple)
