@@ -14,6 +14,7 @@ Reference: ``deepspeed/runtime/zero/stage3.py`` (:73 optimizer, step :2040), ``p
 from __future__ import annotations
 
 import math
+from collections import OrderedDict
 from typing import List, Optional
 
 import torch
@@ -24,6 +25,36 @@ from ..fp16.loss_scaler import CreateLossScaler
 from .optimizer_api import ZeroOptimizerAPI
 from .partition_parameters import (Init, ZeroParamStatus, _partition_param, all_gather_params, is_zero_param, read_partition,
                                    release_partition, set_param_swapper, write_partition)
+
+
+FWD_MODULE_STACK: list = []      # modules whose forward is running (innermost last), kept by the stage-3 hooks
+
+
+class ZeROOrderedDict(OrderedDict):
+    """Stands in for a module's ``_parameters`` under ZeRO-3: reading a partitioned parameter of ANOTHER module while a
+    forward is running (``self.other.weight`` inside ``forward``, tied embeddings used through their owner, ...) gathers
+    it on the spot and registers it as an external parameter of the module that is executing, so it is released with
+    that module and fetched by its hooks from then on (ref: parameter_offload.py:40-75)."""
+
+    def __init__(self, parent_module, *args, **kwargs):
+        super().__init__(*args, **kwargs)
+        self._parent_module = parent_module
+
+    def __reduce__(self):
+        r0, _, *rest = super().__reduce__()
+        return (r0, (self._parent_module, )) + tuple(rest)
+
+    def __getitem__(self, key):
+        param = super().__getitem__(key)
+        if param is None or not FWD_MODULE_STACK:
+            return param
+        if getattr(param, "ds_status", None) == ZeroParamStatus.NOT_AVAILABLE:
+            user = FWD_MODULE_STACK[-1]
+            from .partition_parameters import register_external_parameter
+            register_external_parameter(user, param)
+            all_gather_params([param])
+            param.ds_active_sub_modules.add(id(user))
+        return param
 
 
 class DeepSpeedZeRoOffload:
@@ -92,6 +123,9 @@ class DeepSpeedZeRoOffload:
 
     def _install(self, root: torch.nn.Module):
         self.hooks.append(root.register_forward_pre_hook(self._begin_iteration))
+        for m in root.modules():       # external-parameter detection (see ZeROOrderedDict)
+            if not isinstance(m._parameters, ZeROOrderedDict):
+                m._parameters = ZeROOrderedDict(m, m._parameters)
         under_leaf = set()
         for m in root.modules():
             if id(m) in under_leaf:
@@ -100,8 +134,11 @@ class DeepSpeedZeRoOffload:
                 under_leaf.update(id(c) for c in m.modules() if c is not m)
                 for p in m.parameters():
                     p.ds_z3_leaf_module = m
+            self.hooks.append(m.register_forward_pre_hook(self._push_fwd))
+            self.hooks.append(m.register_forward_hook(self._pop_fwd, always_call=True))
             if not self._own_params(m):
                 continue
+            m._z3_has_param_hooks = True
             self.hooks.append(m.register_forward_pre_hook(self._pre_forward))
             self.hooks.append(m.register_forward_hook(self._post_forward))
             self.hooks.append(m.register_full_backward_pre_hook(self._pre_backward))
@@ -193,6 +230,20 @@ class DeepSpeedZeRoOffload:
         if todo and self._live_numel() + sum(p.ds_numel for p in todo) <= self.max_live_parameters:
             all_gather_params(todo, async_op=True)
             self.stats["prefetched"] += len(todo)
+
+    @staticmethod
+    def _push_fwd(m, args):
+        FWD_MODULE_STACK.append(m)
+
+    def _pop_fwd(self, m, args, out):
+        if FWD_MODULE_STACK and FWD_MODULE_STACK[-1] is m:
+            FWD_MODULE_STACK.pop()
+        ext = getattr(m, "_external_params", None)
+        if ext:
+            # a module that had no parameters of its own when the hooks were installed gets none of the fetch / release
+            # hooks: release what it pulled in through the getter here
+            if not getattr(m, "_z3_has_param_hooks", False):
+                self._release(m)
 
     def _pre_forward(self, m, args):
         ps = self._own_params(m)

@@ -800,3 +800,50 @@ def test_zero3_async_gather_handles_and_quantizer():
     assert torch.nn.Linear in PP.get_all_subclasses(torch.nn.Module) and PP.InsertPostInitMethodToModuleSubClasses is PP.Init
     f = PP.zero_wrapper_for_fp_tensor_constructor(torch.ones, torch.bfloat16)
     assert f(3).dtype == torch.bfloat16 and f(3, dtype=torch.int32).dtype == torch.int32
+
+
+def test_zero3_detects_external_parameters_automatically():
+    """A forward that reads another module's partitioned parameter (``self.other.weight``) triggers the gather through the
+    ``ZeROOrderedDict`` getter and registers the parameter as external - no manual ``register_external_parameter``
+    (ref: parameter_offload.py:40-75)."""
+    import hcache_deepspeed_b200 as ds
+    from hcache_deepspeed_b200.runtime.zero import ZeroParamStatus
+
+    class Tied(torch.nn.Module):
+        def __init__(self, owner):
+            super().__init__()
+            self.__dict__["owner"] = owner                  # not a sub-module: invisible to the hook installer
+
+        def forward(self, h):
+            return h @ self.owner.weight.t()                # reads the embedding's weight
+
+    class Net(torch.nn.Module):
+        def __init__(self):
+            super().__init__()
+            self.emb = torch.nn.Embedding(11, 6)
+            self.mid = torch.nn.Linear(6, 6)
+            self.head = Tied(self.emb)
+
+        def forward(self, ids):
+            return self.head(torch.tanh(self.mid(self.emb(ids)))).pow(2).mean()
+
+    def run(stage):
+        torch.manual_seed(0)
+        engine, _, _, _ = ds.initialize(model=Net(), config={
+            "train_micro_batch_size_per_gpu": 2, "optimizer": {"type": "SGD", "params": {"lr": 0.1}}, "steps_per_print": 1000,
+            "zero_optimization": {"stage": stage, "stage3_param_persistence_threshold": 0}})
+        ids = torch.tensor([[1, 2, 3], [4, 5, 6]])
+        losses = []
+        for _ in range(3):
+            loss = engine(ids)
+            engine.backward(loss)
+            engine.step()
+            losses.append(float(loss))
+        return engine, losses
+
+    e3, l3 = run(3)
+    _, l0 = run(0)
+    assert l3 == pytest.approx(l0, rel=1e-5)
+    w = e3.module.emb.weight
+    assert id(w) in getattr(e3.module.head, "_external_params", {})
+    assert w.ds_status == ZeroParamStatus.NOT_AVAILABLE      # released again after the step
