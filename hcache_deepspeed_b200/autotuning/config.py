@@ -35,3 +35,15 @@ class DeepSpeedAutotuningConfig(DeepSpeedConfigModel):
 
 def get_autotuning_config(param_dict: dict) -> DeepSpeedAutotuningConfig:
     return DeepSpeedAutotuningConfig(**(param_dict.get("autotuning") or {}))
+
+
+def get_default_model_info_config():
+    return {"profile": False, "num_params": None, "hidden_size": None, "num_layers": None}
+
+
+def get_model_info_config(param_dict):
+    """The ``autotuning.model_info`` block over its defaults (``None`` without the block)."""
+    at = param_dict.get("autotuning") or {}
+    if not at.get("model_info"):
+        return None
+    return {**get_default_model_info_config(), **at["model_info"]}

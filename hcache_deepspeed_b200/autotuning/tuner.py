@@ -124,3 +124,74 @@ class ModelBasedTuner(BaseTuner):
 
 # `autotuning.tuner` is a package in the reference; its sub-module paths import through this module (see _import_paths.py)
 __path__: list = []
+
+
+# ---- index <-> feature helpers of the model-based tuner (ref: autotuning/tuner/utils.py) -----------------------------------
+def index_to_feature(p: int, dims) -> List[int]:
+    """A flat index into a grid of sizes ``dims`` -> the coordinate vector (first dimension fastest)."""
+    out = []
+    for d in dims:
+        out.append(p % d)
+        p //= d
+    return out
+
+
+def feature_to_index(feature, dims) -> int:
+    p, stride = 0, 1
+    for k, d in zip(feature, dims):
+        p += stride * int(k)
+        stride *= d
+    return p
+
+
+def dict_to_dims(tuning_space: Dict) -> List[int]:
+    """Number of choices of every leaf of a tuning space, depth first."""
+    dims = []
+    for v in tuning_space.values():
+        if isinstance(v, dict):
+            dims.extend(dict_to_dims(v))
+        else:
+            dims.append(len(v) if isinstance(v, list) else 1)
+    return dims
+
+
+def gen_combinations(d: Dict):
+    """Every assignment of a (nested) space of lists, as dicts, lazily."""
+    import itertools
+    keys = list(d.keys())
+    choices = [list(gen_combinations(v)) if isinstance(v, dict) else (v if isinstance(v, list) else [v]) for v in d.values()]
+    for comb in itertools.product(*choices):
+        yield dict(zip(keys, comb))
+
+
+def dict_to_feature(feature_dict: Dict, keys, max_value=None) -> List[float]:
+    """Numeric feature vector of a config: the values of ``keys`` wherever they occur (booleans as 0/1, strings hashed to
+    their position among the sorted distinct values seen); with ``max_value`` each entry is scaled into [0, 1]."""
+    out = []
+    for k, v in feature_dict.items():
+        if isinstance(v, dict):
+            out.extend(dict_to_feature(v, keys, None))
+        elif k in keys:
+            out.append(float(v) if isinstance(v, (int, float, bool)) else float(abs(hash(str(v))) % 1000))
+    if max_value is not None:
+        out = [x / m if m else x for x, m in zip(out, max_value)]
+    return out
+
+
+class XGBoostCostModel:
+    """Name kept for configs that ask for the reference's cost model; the model-based tuner here fits a ridge regression
+    on the flattened config features (no xgboost in this image), behind the same ``fit`` / ``predict`` pair."""
+
+    def __init__(self, loss_type: str = "reg", num_threads=None, log_interval: int = 25, upper_model=None):
+        self.w = None
+
+    def fit(self, xs, ys):
+        x = np.asarray(xs, dtype=np.float64)
+        y = np.asarray(ys, dtype=np.float64)
+        x1 = np.concatenate([x, np.ones((x.shape[0], 1))], axis=1)
+        self.scale = max(float(np.abs(y).max()), 1e-9)      # targets are fitted in units of their largest magnitude
+        self.w = np.linalg.solve(x1.T @ x1 + 1e-6 * np.eye(x1.shape[1]), x1.T @ (y / self.scale))
+
+    def predict(self, xs):
+        x = np.asarray(xs, dtype=np.float64)
+        return (np.concatenate([x, np.ones((x.shape[0], 1))], axis=1) @ self.w) * self.scale

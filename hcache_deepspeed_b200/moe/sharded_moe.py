@@ -285,3 +285,20 @@ class MOELayer(torch.nn.Module):
         if timed:
             self.time_moe = self._now(x) - t0
         return combined.reshape(x.shape)
+
+
+def einsum(rule: str, a: Tensor, b: Tensor) -> Tensor:
+    """The handful of contractions the MoE layer uses, as explicit matmuls / broadcasts where that is faster than
+    ``torch.einsum`` (dispatch / combine are batched matmuls); anything else falls through to ``torch.einsum``."""
+    if rule == "s,se->se":
+        return a.unsqueeze(1) * b
+    if rule == "se,sc->sec":
+        return a.unsqueeze(2) * b.unsqueeze(1)
+    if rule == "se,se->s":
+        return (a * b).sum(dim=1)
+    if rule == "sec,sm->ecm":
+        s = a.shape[0]
+        return torch.matmul(a.reshape(s, -1).t(), b).reshape(a.shape[1], a.shape[2], b.shape[1])
+    if rule == "sec,ecm->sm":
+        return torch.matmul(a.reshape(a.shape[0], -1), b.reshape(-1, b.shape[-1]))
+    return torch.einsum(rule, a, b)

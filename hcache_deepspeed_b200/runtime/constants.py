@@ -52,3 +52,5 @@ TRAIN_BATCH_SIZE_EXAMPLE = {"train_batch_size": 32}
 def defaults() -> dict:
     """``key -> default`` of every scalar top-level key."""
     return {k: d for k, d in _KEYS.items() if d is not None}
+
+from .config_getters import ValidationMode  # noqa: E402,F401

@@ -86,3 +86,41 @@ def get_curriculum_params_legacy(param_dict: dict):
         return False
     sec.pop(C.CURRICULUM_LEARNING_ENABLED, None)
     return sec
+
+
+# ---- single-entry readers (ref: data_pipeline/config.py:59-193) ---------------------------------------------------------------
+def _sub(param_dict, section, key, default):
+    return (param_dict.get(section) or {}).get(key, default)
+
+
+def get_data_sampling_num_epochs(param_dict):
+    return _sub(param_dict, "data_sampling", "num_epochs", 1000)
+
+
+def get_data_sampling_num_workers(param_dict):
+    return _sub(param_dict, "data_sampling", "num_workers", 0)
+
+
+def get_data_sampling_pin_memory(param_dict):
+    return _sub(param_dict, "data_sampling", "pin_memory", False)
+
+
+def get_curriculum_learning_enabled(param_dict):
+    return bool(_sub(param_dict, "curriculum_learning", "enabled", False))
+
+
+def _params_of(param_dict, section):
+    import copy
+    if section not in param_dict:
+        return {}
+    out = copy.copy(param_dict[section])
+    out.pop("enabled", None)
+    return out
+
+
+def get_curriculum_learning_params(param_dict):
+    return _params_of(param_dict, "curriculum_learning")
+
+
+def get_random_ltd_params(param_dict):
+    return _params_of(param_dict, "random_ltd")

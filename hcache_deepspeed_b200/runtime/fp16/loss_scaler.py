@@ -92,3 +92,7 @@ def CreateLossScaler(dtype, static_loss_scale, dynamic_scaling, dynamic_loss_arg
     if dtype == torch.half and dynamic_scaling:
         return DynamicLossScaler(dtype=dtype, **(dynamic_loss_args or {}))
     return LossScaler(scale=static_loss_scale if dtype == torch.half else 1.0)
+
+
+def to_python_float(t):
+    return t.item() if hasattr(t, "item") else t[0]

@@ -422,3 +422,7 @@ class PipelineEngine(DeepSpeedEngine):
                                            exclude_frozen_parameters=exclude_frozen_parameters)
         finally:
             self._curr_ckpt_path = None
+
+
+def is_even(number: int) -> bool:
+    return number % 2 == 0

@@ -18,3 +18,12 @@ class ZeroStageEnum(IntEnum):
 
 def read_zero_config_deprecated(param_dict):
     return {"stage": 1 if param_dict.get("zero_optimization") else 0}
+
+
+def get_zero_config(param_dict):
+    """The typed ``zero_optimization`` block of a raw config dict (a bare ``true`` means stage 1, as of old)."""
+    from ..config import ZeroConfig
+    block = param_dict.get("zero_optimization", {})
+    if isinstance(block, bool):
+        block = {"stage": 1 if block else 0}
+    return ZeroConfig(**block)

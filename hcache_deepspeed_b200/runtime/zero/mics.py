@@ -82,3 +82,9 @@ class MiCS_Optimizer(DeepSpeedZeroOptimizer_Stage3):
                 dist.all_reduce(t, group=g.param_repli_group)
                 t.div_(g.param_repli_size)
         return super().step(closure)
+
+
+def scale_tensors(tensors, scale) -> None:
+    """Divide every tensor in place (averaging after a summed collective)."""
+    for t in tensors:
+        t.div_(scale)
