@@ -113,3 +113,19 @@ class CCLBackend(TorchBackend):
             if shm.attached(g) is not None:
                 shm.detach(g)
         shm.route_all_collectives = False
+
+
+def build_ccl_op():
+    """The native host-collectives library behind ``CCLBackend`` (oneCCL in the reference, the shared-memory engine here)."""
+    from .torch import build_shm_op
+    return build_shm_op()
+
+
+class CCLHandler:
+    """Completion handle of a host collective: they complete before returning, so ``wait`` has nothing left to do."""
+
+    def __init__(self, ccl_comm_op=None):
+        self.ccl_comm_op = ccl_comm_op
+
+    def wait(self):
+        return None

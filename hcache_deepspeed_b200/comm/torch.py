@@ -84,10 +84,102 @@ class TorchBackend(Backend):
         return _c.enable_symm_mem_for_group(group_name)
 
 
+# ---- switches that turn whole families of collectives into no-ops on this backend object (ref: comm/torch.py:20-110): a
+#      way to measure how much of a step is communication. A switched-off call returns ``Noop``, whose ``wait()`` returns.
+DS_COMM_ALL_GATHER_OFF = False
+DS_COMM_REDUCE_SCATTER_OFF = False
+DS_COMM_BROADCAST_OFF = False
+DS_COMM_ALL_REDUCE_OFF = False
+DS_COMM_REDUCE_OFF = False
+
+
+class Noop:
+
+    def wait(self, *args, **kwargs):
+        return None
+
+    def is_completed(self) -> bool:
+        return True
+
+
+def all_gather_comm_off(flag: bool = False) -> None:
+    global DS_COMM_ALL_GATHER_OFF
+    DS_COMM_ALL_GATHER_OFF = flag
+
+
+def reduce_scatter_comm_off(flag: bool = False) -> None:
+    global DS_COMM_REDUCE_SCATTER_OFF
+    DS_COMM_REDUCE_SCATTER_OFF = flag
+
+
+def broadcast_comm_off(flag: bool = False) -> None:
+    global DS_COMM_BROADCAST_OFF
+    DS_COMM_BROADCAST_OFF = flag
+
+
+def all_reduce_comm_off(flag: bool = False) -> None:
+    global DS_COMM_ALL_REDUCE_OFF
+    DS_COMM_ALL_REDUCE_OFF = flag
+
+
+def reduce_comm_off(flag: bool = False) -> None:
+    global DS_COMM_REDUCE_OFF
+    DS_COMM_REDUCE_OFF = flag
+
+
+def backward_comm_off(flag: bool = False) -> None:
+    """The two collectives of a data-parallel backward pass (gradient reduce-scatter / parameter all-gather) off or on."""
+    all_gather_comm_off(flag)
+    reduce_scatter_comm_off(flag)
+
+
+def _switched_off(name: str) -> bool:
+    if name.startswith("all_gather"):
+        return DS_COMM_ALL_GATHER_OFF
+    if name.startswith("reduce_scatter"):
+        return DS_COMM_REDUCE_SCATTER_OFF
+    if name == "broadcast":
+        return DS_COMM_BROADCAST_OFF
+    if name in ("all_reduce", "inference_all_reduce", "all_reduce_coalesced"):
+        return DS_COMM_ALL_REDUCE_OFF
+    if name == "reduce":
+        return DS_COMM_REDUCE_OFF
+    return False
+
+
+def disable_compiler_collective(func):
+    """No tracing compiler runs over this package's collectives: the decorator is the identity."""
+    return func
+
+
+def has_coalescing_manager() -> bool:
+    return hasattr(tdist, "distributed_c10d") and hasattr(tdist.distributed_c10d, "_coalescing_manager")
+
+
+def has_all_reduce_coalesced() -> bool:
+    return hasattr(tdist, "all_reduce_coalesced")
+
+
+def build_shm_op():
+    """The host collectives engine (C++ over POSIX shared memory) as a loaded library, or ``None`` when it cannot be
+    built here."""
+    try:
+        from ..ops.op_builder import ALL_OPS
+        b = ALL_OPS.get("shm_comm") or ALL_OPS.get("deepspeed_shm_comm")
+        return b.load() if b is not None and not b.compatibility_problems() else None
+    except Exception:
+        return None
+
+
 def _delegate(name):
     fn = getattr(_c, name)
 
     def method(self, *a, **k):
+        if _switched_off(name):
+            if int(os.environ.get("RANK", "0")) == 0:
+                from ..utils.logging import logger
+                logger.warning(f"{name} is OFF")
+            return Noop()
         return fn(*a, **k)
 
     method.__name__ = name

@@ -316,3 +316,25 @@ def ulysses_engine_worker(rank, world):
             engine.backward(l); engine.step()
             t = l.detach().clone() / world; torch.distributed.all_reduce(t); got.append(round(float(t), 5))
         return {"want": want, "got": got, "dp": engine.dp_world_size, "sp": engine.sequence_parallel_size}
+
+
+def comm_off_worker(rank, world):
+    """The switches that turn families of collectives into no-ops on a backend object (ref: comm/torch.py:60-110)."""
+    import importlib
+    import torch
+    import hcache_deepspeed_b200 as ds
+    ds.init_distributed(dist_backend="gloo")
+    T = importlib.import_module("hcache_deepspeed_b200.comm.torch")
+    b = T.TorchBackend(backend="gloo")
+    t = torch.full((2, ), float(rank + 1))
+    T.all_reduce_comm_off(True)
+    off = b.all_reduce(t)
+    skipped = t.tolist()
+    T.all_reduce_comm_off(False)
+    b.all_reduce(t)
+    T.backward_comm_off(True)
+    flags = (T.DS_COMM_ALL_GATHER_OFF, T.DS_COMM_REDUCE_SCATTER_OFF)
+    gathered = b.all_gather_into_tensor(torch.zeros(2 * world), torch.ones(2))
+    T.backward_comm_off(False)
+    return {"noop": type(off).__name__, "wait": off.wait(), "skipped": skipped, "reduced": t.tolist(), "flags": flags,
+            "gather_noop": type(gathered).__name__, "probes": (T.has_all_reduce_coalesced(), T.has_coalescing_manager())}

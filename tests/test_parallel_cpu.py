@@ -175,3 +175,10 @@ def test_moe_wall_clock_breakdown_counters_and_engine_report():
     rep = engine.print_forward_breakdown(fwd_time=12.5)
     assert rep["fwd"] == 12.5 and rep["fwd_moe"] == pytest.approx(sum(l.time_moe for l in layers))
     assert rep["top_k"] == pytest.approx(sum(l.gate_time for l in layers)) and rep["1st_a2a"] >= 0.0
+
+
+def test_comm_off_switches_2ranks():
+    from tests.parallel_helper import comm_off_worker
+    for rank, r in enumerate(run_distributed(comm_off_worker, 2)):
+        assert r["noop"] == "Noop" and r["wait"] is None and r["skipped"] == [rank + 1.0] * 2 and r["reduced"] == [3.0, 3.0], r
+        assert r["flags"] == (True, True) and r["gather_noop"] == "Noop" and r["probes"][0] is True, r
