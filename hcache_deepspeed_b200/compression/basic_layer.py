@@ -365,3 +365,148 @@ class BNLayer_Compress(nn.BatchNorm2d):
         self.bias = nn.Parameter(self.bias.data[mask])
         self.running_mean, self.running_var = self.running_mean[mask], self.running_var[mask]
         self.num_features = int(mask.sum())
+
+
+# ---- Megatron-style model-parallel variants (ref: basic_layer.py:680-840) -----------------------------------------------------
+g_mpu = None
+
+
+def split_tensor_along_last_dim(tensor, num_partitions: int, contiguous_split_chunks: bool = False):
+    assert tensor.shape[-1] % num_partitions == 0, f"{tensor.shape[-1]} is not divisible by {num_partitions}"
+    parts = torch.split(tensor, tensor.shape[-1] // num_partitions, dim=-1)
+    return tuple(p.contiguous() for p in parts) if contiguous_split_chunks else parts
+
+
+def _mp():
+    from .. import comm as dist
+    group = g_mpu.get_model_parallel_group()
+    return dist, group, dist.get_world_size(group=group), dist.get_rank(group=group)
+
+
+class _CopyToMP(torch.autograd.Function):
+    """Identity forward, all-reduce of the gradient backward (input of a column-parallel layer)."""
+
+    @staticmethod
+    def forward(ctx, x):
+        return x
+
+    @staticmethod
+    def backward(ctx, g):
+        dist, group, ws, _ = _mp()
+        if ws > 1:
+            g = g.contiguous()
+            dist.all_reduce(g, group=group)
+        return g
+
+
+class _ReduceFromMP(torch.autograd.Function):
+    """All-reduce forward, identity backward (output of a row-parallel layer)."""
+
+    @staticmethod
+    def forward(ctx, x):
+        dist, group, ws, _ = _mp()
+        if ws > 1:
+            x = x.contiguous().clone()
+            dist.all_reduce(x, group=group)
+        return x
+
+    @staticmethod
+    def backward(ctx, g):
+        return g
+
+
+class _ScatterToMP(torch.autograd.Function):
+    """Keep this rank's slice of the last dimension forward, all-gather the gradient backward."""
+
+    @staticmethod
+    def forward(ctx, x):
+        _, _, ws, rank = _mp()
+        return x if ws == 1 else split_tensor_along_last_dim(x, ws)[rank].contiguous()
+
+    @staticmethod
+    def backward(ctx, g):
+        return _gather_last(g)
+
+
+class _GatherFromMP(torch.autograd.Function):
+    """All-gather along the last dimension forward, keep this rank's slice of the gradient backward."""
+
+    @staticmethod
+    def forward(ctx, x):
+        return _gather_last(x)
+
+    @staticmethod
+    def backward(ctx, g):
+        _, _, ws, rank = _mp()
+        return g if ws == 1 else split_tensor_along_last_dim(g, ws)[rank].contiguous()
+
+
+def _gather_last(x):
+    dist, group, ws, rank = _mp()
+    if ws == 1:
+        return x
+    parts = [torch.empty_like(x) for _ in range(ws)]
+    parts[rank] = x.contiguous()
+    dist.all_gather(parts, parts[rank], group=group)
+    return torch.cat(parts, dim=-1).contiguous()
+
+
+def copy_to_model_parallel_region(input_):
+    return _CopyToMP.apply(input_)
+
+
+def reduce_from_model_parallel_region(input_):
+    return _ReduceFromMP.apply(input_)
+
+
+def scatter_to_model_parallel_region(input_):
+    return _ScatterToMP.apply(input_)
+
+
+def gather_from_model_parallel_region(input_):
+    return _GatherFromMP.apply(input_)
+
+
+class ColumnParallelLinear_Compress(LinearLayer_Compress):
+    """Compressible linear whose OUTPUT features are split over the model-parallel group of ``mpu``; returns
+    ``(output, bias or None)`` like Megatron's layer (``skip_bias_add`` hands the bias back unapplied)."""
+
+    def __init__(self, mpu, input_size: int, output_size: int, bias: bool = True, gather_output: bool = True,
+                 skip_bias_add: bool = False):
+        global g_mpu
+        g_mpu = mpu
+        ws = mpu.get_model_parallel_world_size()
+        assert output_size % ws == 0
+        self.input_size, self.output_size, self.gather_output, self.skip_bias_add = input_size, output_size, gather_output, skip_bias_add
+        self.output_size_per_partition = output_size // ws
+        super().__init__(input_size, self.output_size_per_partition, bias=bias)
+
+    def forward(self, input_):
+        x = copy_to_model_parallel_region(input_)
+        if self.skip_bias_add:
+            out, bias = super().forward(x, True)
+        else:
+            out, bias = super().forward(x), None
+        return (gather_from_model_parallel_region(out) if self.gather_output else out), bias
+
+
+class RowParallelLinear_Compress(LinearLayer_Compress):
+    """Compressible linear whose INPUT features are split over the model-parallel group; partial products are summed."""
+
+    def __init__(self, mpu, input_size: int, output_size: int, bias: bool = True, input_is_parallel: bool = False,
+                 skip_bias_add: bool = False):
+        global g_mpu
+        g_mpu = mpu
+        ws = mpu.get_model_parallel_world_size()
+        assert input_size % ws == 0
+        self.input_size, self.output_size, self.input_is_parallel, self.skip_bias_add = input_size, output_size, input_is_parallel, skip_bias_add
+        self.input_size_per_partition = input_size // ws
+        super().__init__(self.input_size_per_partition, output_size, bias=bias)
+
+    def forward(self, input_):
+        x = input_ if self.input_is_parallel else scatter_to_model_parallel_region(input_)
+        partial, bias = super().forward(x, True)
+        out = reduce_from_model_parallel_region(partial)
+        if not self.skip_bias_add:
+            return (out + bias if bias is not None else out), None
+        return out, bias

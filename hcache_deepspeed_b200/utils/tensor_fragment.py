@@ -347,3 +347,82 @@ def safe_set_local_optimizer_state(param, value: torch.Tensor, optim_state_key: 
                 st[optim_state_key].data.narrow(0, off, param.ds_partition_numel).copy_(value.reshape(-1))
         return
     safe_set_full_optimizer_state(param, value, optim_state_key, optimizer)
+
+
+# ---- the fragment-linkage form of the accessors (ref: tensor_fragment.py:13-130, 312): functions that take the low-precision
+#      parameter as ``self`` - ``link_hp_params`` binds them as methods for optimizers that keep ``_hp_mapping`` fragments --------
+from .mixed_precision_linkage import fragment_address, get_hp_fragment_mapping, tensor_fragment  # noqa: E402,F401
+
+
+def _frag_full(self, pick) -> torch.Tensor:
+    """Every rank writes its fragment into a zero buffer of the parameter's size; the sum over the group is the tensor."""
+    buf = torch.zeros(self.numel(), dtype=torch.float32, device=self.device)
+    m = getattr(self, "_hp_mapping", None)
+    if m is not None:
+        a = m.lp_fragment_address
+        buf.narrow(0, a.start, a.numel).copy_(pick(m).detach().float().reshape(-1))
+    group = getattr(self, "_dp_group", None)
+    if dist.is_initialized() and dist.get_world_size(group=group) > 1:
+        dist.all_reduce(buf, group=group)
+    return buf.reshape(self.shape)
+
+
+def get_full_hp_param(self, optim_state_key=None):
+    """Full fp32 value (or optimizer state ``optim_state_key``) of a parameter whose master copy is spread over the group
+    as ``_hp_mapping`` fragments; parameters without the linkage go through ``safe_get_full_*``."""
+    if not hasattr(self, "_hp_mapping"):
+        return safe_get_full_fp32_param(self) if optim_state_key is None else safe_get_full_optimizer_state(self, optim_state_key)
+    return _frag_full(self, lambda m: m.get_hp_fragment(optim_state_key))
+
+
+def set_full_hp_param(self, value, optim_state_key=None) -> None:
+    if not hasattr(self, "_hp_mapping"):
+        if optim_state_key is None:
+            return safe_set_full_fp32_param(self, value)
+        return safe_set_full_optimizer_state(self, value, optim_state_key)
+    m = self._hp_mapping
+    if m is not None:
+        a = m.lp_fragment_address
+        m.get_hp_fragment(optim_state_key).data.copy_(value.reshape(-1).narrow(0, a.start, a.numel).to(m.hp_fragment.dtype))
+
+
+def _lp_grad_fragment(self):
+    m = self._hp_mapping
+    grads = getattr(m, "gradient_dict", None)
+    if grads and m.param_group_index in grads and grads[m.param_group_index] is not None:
+        return grads[m.param_group_index][self._index_in_param_group]
+    if self.grad is None:
+        raise ValueError("Gradients are only available immediately after backward and before engine step")
+    a = m.lp_fragment_address
+    return self.grad.reshape(-1).narrow(0, a.start, a.numel)
+
+
+def get_full_hp_grad(self):
+    if not hasattr(self, "_hp_mapping"):
+        return safe_get_full_grad(self)
+    return _frag_full(self, lambda m: _lp_grad_fragment(self)) if self._hp_mapping is not None else _frag_full(self, None)
+
+
+def set_full_hp_grad(self, value) -> None:
+    if not hasattr(self, "_hp_mapping"):
+        return safe_set_full_grad(self, value)
+    if self._hp_mapping is not None:
+        frag = _lp_grad_fragment(self)
+        a = self._hp_mapping.lp_fragment_address
+        frag.data.copy_(value.reshape(-1).narrow(0, a.start, a.numel).reshape(frag.shape).to(frag.dtype))
+
+
+def map_to_flat_opt_states(flat_hp_tensor, lp_tensors, optim_state, opt_keys) -> None:
+    """Rebuild the flat optimizer-state tensors ``optim_state[flat_hp_tensor][key]`` from the fragments the low-precision
+    parameters hold, and re-point the fragments into the new flat buffers."""
+    for key in opt_keys:
+        buf = torch.zeros_like(flat_hp_tensor)
+        for lp in lp_tensors:
+            m = getattr(lp, "_hp_mapping", None)
+            if m is None:
+                continue
+            a = m.hp_fragment_address
+            piece = buf.narrow(0, a.start, a.numel)
+            piece.copy_(m.get_hp_fragment(optim_state_key=key).data)
+            m.optim_fragment[key] = piece
+        optim_state[flat_hp_tensor][key] = buf

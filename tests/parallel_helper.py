@@ -338,3 +338,44 @@ def comm_off_worker(rank, world):
     T.backward_comm_off(False)
     return {"noop": type(off).__name__, "wait": off.wait(), "skipped": skipped, "reduced": t.tolist(), "flags": flags,
             "gather_noop": type(gathered).__name__, "probes": (T.has_all_reduce_coalesced(), T.has_coalescing_manager())}
+
+
+def mp_compress_worker(rank, world):
+    """Column- then row-parallel compressible linears over a model-parallel group equal a dense two-layer product,
+    forward and input gradient (ref: compression/basic_layer.py:680-840)."""
+    import torch
+    import hcache_deepspeed_b200 as ds
+    from hcache_deepspeed_b200.compression import basic_layer as BL
+    ds.init_distributed(dist_backend="gloo")
+    group = ds.comm.new_group(list(range(world)))
+
+    class Mpu:
+        def get_model_parallel_group(self):
+            return group
+
+        def get_model_parallel_world_size(self):
+            return world
+
+        def get_model_parallel_rank(self):
+            return rank
+
+    torch.manual_seed(0)
+    w1, b1, w2, b2 = torch.randn(8, 6), torch.randn(8), torch.randn(4, 8), torch.randn(4)
+    col = BL.ColumnParallelLinear_Compress(Mpu(), 6, 8, gather_output=False)
+    row = BL.RowParallelLinear_Compress(Mpu(), 8, 4, input_is_parallel=True)
+    with torch.no_grad():
+        col.weight.copy_(w1.chunk(world, 0)[rank]); col.bias.copy_(b1.chunk(world, 0)[rank])
+        row.weight.copy_(w2.chunk(world, 1)[rank]); row.bias.copy_(b2)
+    x = torch.randn(3, 6, requires_grad=True)
+    h, _ = col(x)
+    y, _ = row(torch.tanh(h))
+    y.pow(2).sum().backward()
+    xr = x.detach().clone().requires_grad_(True)
+    yr = torch.tanh(xr @ w1.t() + b1) @ w2.t() + b2
+    yr.pow(2).sum().backward()
+    full = BL.ColumnParallelLinear_Compress(Mpu(), 6, 8, gather_output=True, skip_bias_add=True)
+    out, bias = full(x.detach())
+    sc = BL.scatter_to_model_parallel_region(torch.arange(8.).reshape(1, 8))
+    return {"fwd": float((y - yr).abs().max()), "grad": float((x.grad - xr.grad).abs().max()),
+            "gathered_shape": tuple(out.shape), "bias_back": bias is not None and tuple(bias.shape) == (8 // world, ),
+            "scatter": sc.tolist(), "gather": BL.gather_from_model_parallel_region(sc).tolist()}

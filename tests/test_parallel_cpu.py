@@ -182,3 +182,10 @@ def test_comm_off_switches_2ranks():
     for rank, r in enumerate(run_distributed(comm_off_worker, 2)):
         assert r["noop"] == "Noop" and r["wait"] is None and r["skipped"] == [rank + 1.0] * 2 and r["reduced"] == [3.0, 3.0], r
         assert r["flags"] == (True, True) and r["gather_noop"] == "Noop" and r["probes"][0] is True, r
+
+
+def test_model_parallel_compress_layers_2ranks():
+    from tests.parallel_helper import mp_compress_worker
+    for rank, r in enumerate(run_distributed(mp_compress_worker, 2)):
+        assert r["fwd"] < 1e-5 and r["grad"] < 1e-4 and r["gathered_shape"] == (3, 8) and r["bias_back"], r
+        assert r["scatter"] == [[4.0 * rank + i for i in range(4)]] and r["gather"] == [[float(i) for i in range(8)]], r
