@@ -77,12 +77,12 @@ ALIASES = {
     "runtime.data_pipeline.data_routing.helper": [("runtime.data_pipeline.random_ltd", "convert_to_random_ltd", "convert_to_random_ltd"), ("runtime.data_pipeline.random_ltd", "remove_random_ltd_state_dict", "remove_random_ltd_state_dict"), ("runtime.data_pipeline.random_ltd", "save_without_random_ltd", "save_without_random_ltd")],
     "runtime.data_pipeline.data_sampling.data_sampler": [("runtime.data_pipeline.data_sampler", "DeepSpeedDataSampler", "DeepSpeedDataSampler")],
     "runtime.fp16.unfused_optimizer": [("runtime.fp16.fused_optimizer", "FP16_UnfusedOptimizer", "FP16_UnfusedOptimizer")],
-    "runtime.zero.mics_utils": [("runtime.zero.mics", "MiCS_CommGroups", "MiCS_CommGroups"), ("runtime.zero.mics", "create_mics_comm_groups", "create_mics_comm_groups"), ("runtime.zero.mics", "mics_group_ranks", "mics_group_ranks"), ("runtime.zero.mics", "scale_tensors", "scale_tensors")],
+    "runtime.zero.mics_utils": [("runtime.zero.mics", "MiCS_CommGroups", "MiCS_CommGroups"), ("runtime.zero.mics", "create_mics_comm_groups", "create_mics_comm_groups"), ("runtime.zero.mics", "mics_group_ranks", "mics_group_ranks"), ("runtime.zero.mics", "scale_tensors", "scale_tensors"), ("runtime.zero.mics", "has_hierarchical_all_gather_groups", "has_hierarchical_all_gather_groups")],
     "runtime.zero.offload_config": [("runtime.zero.config", "*", "*"), ("runtime.zero.offload_states", "OffloadStateTypeEnum", "OffloadStateTypeEnum")],
     "runtime.zero.parameter_offload": [("runtime.zero.stage3", "DeepSpeedZeRoOffload", "DeepSpeedZeRoOffload"), ("runtime.zero.stage3", "ZeROOrderedDict", "ZeROOrderedDict"), ("runtime.zero.stage3", "FWD_MODULE_STACK", "FWD_MODULE_STACK")],
     "autotuning.tuner.utils": [("autotuning.tuner", n, n) for n in ("index_to_feature", "feature_to_index", "dict_to_dims", "gen_combinations", "flatten", "dict_to_feature")],
     "autotuning.tuner.cost_model": [("autotuning.tuner", "XGBoostCostModel", "XGBoostCostModel")],
-    "runtime.zero.partitioned_param_coordinator": [("runtime.zero.partition_parameters", "all_gather_params", "all_gather_params"), ("runtime.zero.stage3", "DeepSpeedZeRoOffload", "PartitionedParameterCoordinator")],
+    "runtime.zero.partitioned_param_coordinator": [("runtime.zero.partition_parameters", "all_gather_params", "all_gather_params"), ("runtime.zero.stage3", "DeepSpeedZeRoOffload", "PartitionedParameterCoordinator")] + [("runtime.zero.stage3", n, n) for n in ("ZeRoTraceMode", "InflightParamRegistry", "get_all_parameters", "iter_params")] + [("runtime.zero.partition_parameters", "debug_rank0", "debug_rank0")],
     "utils.comms_logging": [("comm.comms_logging", "*", "*"), ("comm.comms_logging", "CommsLogger", "CommsLogger")],
 }
 

@@ -403,3 +403,11 @@ def _patch_alibi_builders(model: nn.Module, mp_size: int, rank: int) -> None:
             def build(attention_mask, num_heads, dtype, _m=m):
                 return build_bloom_alibi_tensor(attention_mask, num_heads, dtype, mp_size=mp_size, mp_rank=rank)
             m.build_alibi_tensor = build
+
+
+def move(tensor: torch.Tensor, device, copy: bool = True) -> torch.Tensor:
+    """A shard on its target device as its OWN storage (``copy=True`` even for cpu -> cpu), so that the full tensor it was
+    cut from can be freed; meta tensors become uninitialised tensors of the same shape."""
+    if tensor.is_meta:
+        return torch.empty_like(tensor, device=device)
+    return tensor.to(device, copy=copy)

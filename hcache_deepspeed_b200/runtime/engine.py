@@ -1259,3 +1259,17 @@ def initialize(args=None, model: torch.nn.Module = None, optimizer=None, model_p
                                  dist_init_required=dist_init_required, collate_fn=collate_fn, config=config,
                                  config_class=cfg)
     return engine, engine.optimizer, engine.training_dataloader, engine.lr_scheduler
+
+
+def split_half_float_double_sparse(tensors):
+    """Gradients grouped for reduction: ([(dtype, [SparseTensor...])...], [(dtype, [dense tensor...])...])."""
+    from .sparse_tensor import SparseTensor
+    sparse, dense = [], []
+    for dtype in (torch.float16, torch.bfloat16, torch.float32, torch.float64):
+        sp = [t for t in tensors if isinstance(t, SparseTensor) and t.dtype == dtype]
+        de = [t for t in tensors if not isinstance(t, SparseTensor) and t.dtype == dtype]
+        if sp:
+            sparse.append((dtype, sp))
+        if de:
+            dense.append((dtype, de))
+    return sparse, dense

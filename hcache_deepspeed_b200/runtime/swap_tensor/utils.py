@@ -148,3 +148,24 @@ class SwapBufferManager:
         for b in buffers:
             i = self.used_buffer_index.pop(id(b))
             self.free_buffer_index.append(i)
+
+
+def swap_in_tensors(swap_handle, tensor_buffers, swap_paths) -> None:
+    """Queue one read per (buffer, file) on an AIO handle; the caller waits on the handle."""
+    for buf, path in zip(tensor_buffers, swap_paths):
+        rc = swap_handle.async_pread(buf, path)
+        assert rc in (0, None), f"async_pread({path}) failed: {rc}"
+
+
+def swap_out_tensors(swap_handle, tensor_buffers, swap_paths) -> None:
+    for buf, path in zip(tensor_buffers, swap_paths):
+        rc = swap_handle.async_pwrite(buf, path)
+        assert rc in (0, None), f"async_pwrite({path}) failed: {rc}"
+
+
+def print_object(obj, name: str, exclude_list=()) -> None:
+    from ...utils.logging import logger
+    logger.info(f"{name}:")
+    for arg in sorted(vars(obj)):
+        if arg not in exclude_list:
+            logger.info(f"  {arg} {'.' * max(1, 29 - len(arg))} {getattr(obj, arg)}")

@@ -11,7 +11,8 @@ import torch
 
 from ... import comm as dist
 from .partition_parameters import Init
-from .stage3 import DeepSpeedZeroOptimizer_Stage3
+from .partition_parameters import AllGatherCoalescedHandle
+from .stage3 import DeepSpeedZeRoOffload, DeepSpeedZeroOptimizer_Stage3
 
 
 @dataclass
@@ -46,7 +47,47 @@ def create_mics_comm_groups(shard_size: int, dp_group=None, hierarchical_allgath
         grp = dist.new_group(ranks)
         if me in ranks:
             g.param_repli_group, g.param_repli_size, g.param_repli_rank = grp, len(ranks), ranks.index(me)
+    node = _node_size()
+    if hierarchical_allgather and shard_size > node and shard_size % node == 0:
+        # a shard group that spans nodes: gather across nodes among ranks of equal local index first (few large messages
+        # over the network), then inside each node (NVLink) - ref: mics_utils.py create_mics_comm_groups
+        for ranks in shard:
+            for lo in range(0, shard_size, node):
+                intra = ranks[lo:lo + node]
+                grp = dist.new_group(intra)
+                if me in intra:
+                    g.param_intra_node_group = grp
+            for off in range(node):
+                inter = ranks[off::node]
+                grp = dist.new_group(inter)
+                if me in inter:
+                    g.param_inter_node_shard_group = grp
     return g
+
+
+def _node_size() -> int:
+    import os
+    for key in ("HDS_MICS_NODE_SIZE", "LOCAL_WORLD_SIZE"):
+        if os.environ.get(key):
+            return int(os.environ[key])
+    return max(1, torch.cuda.device_count()) if torch.cuda.is_available() else 1
+
+
+def hierarchical_all_gather(local: torch.Tensor, comm_groups: MiCS_CommGroups) -> torch.Tensor:
+    """All-gather of equal slices over a shard group in two hops (inter-node among equal local indices, then intra-node),
+    returned in shard-rank order. Falls back to one all-gather without the hierarchical groups."""
+    flat = local.contiguous().view(-1)
+    if not has_hierarchical_all_gather_groups(comm_groups):
+        out = torch.empty(flat.numel() * comm_groups.param_shard_size, dtype=flat.dtype, device=flat.device)
+        dist.all_gather_into_tensor(out, flat, group=comm_groups.param_shard_group)
+        return out
+    n_nodes = dist.get_world_size(group=comm_groups.param_inter_node_shard_group)
+    node = dist.get_world_size(group=comm_groups.param_intra_node_group)
+    across = torch.empty(flat.numel() * n_nodes, dtype=flat.dtype, device=flat.device)
+    dist.all_gather_into_tensor(across, flat, group=comm_groups.param_inter_node_shard_group)   # [node j] slices of my local index
+    both = torch.empty(across.numel() * node, dtype=flat.dtype, device=flat.device)
+    dist.all_gather_into_tensor(both, across, group=comm_groups.param_intra_node_group)          # [local i][node j]
+    return both.view(node, n_nodes, -1).transpose(0, 1).reshape(-1)                             # -> [node j][local i] = rank order
 
 
 class MiCS_Init(Init):
@@ -75,16 +116,38 @@ class MiCS_Optimizer(DeepSpeedZeroOptimizer_Stage3):
         super().__init__(module, init_optimizer, *args, **kwargs)
 
     @torch.no_grad()
-    def step(self, closure=None):
+    def allreduce_mics_shard_grads(self, partitioned_grads=None) -> None:
+        """Average this rank's gradient slices with the ranks that hold the same slices in the other replica groups."""
         g = self.mics_comm_groups
-        if g is not None and g.param_repli_size > 1:
-            for t in self.grad_partitions.values():
-                dist.all_reduce(t, group=g.param_repli_group)
-                t.div_(g.param_repli_size)
+        if g is None or g.param_repli_size <= 1:
+            return
+        grads = list(partitioned_grads) if partitioned_grads is not None else list(self.grad_partitions.values())
+        for t in grads:
+            dist.all_reduce(t, group=g.param_repli_group)
+        scale_tensors(grads, g.param_repli_size)
+
+    @torch.no_grad()
+    def step(self, closure=None):
+        self.allreduce_mics_shard_grads()
         return super().step(closure)
+
+
+class MiCS_Offload(DeepSpeedZeRoOffload):
+    """The stage-3 hook installer over MiCS-partitioned parameters (their process group is the shard group, so the fetch
+    / release logic is the base class's)."""
 
 
 def scale_tensors(tensors, scale) -> None:
     """Divide every tensor in place (averaging after a summed collective)."""
     for t in tensors:
         t.div_(scale)
+
+
+def has_hierarchical_all_gather_groups(comm_groups) -> bool:
+    """Were both the intra-node group and the inter-node shard group created (the two-hop gather is possible)?"""
+    return getattr(comm_groups, "param_intra_node_group", None) is not None and \
+        getattr(comm_groups, "param_inter_node_shard_group", None) is not None
+
+
+class MiCS_AllGatherCoalescedHandle(AllGatherCoalescedHandle):   # noqa: F811
+    """Handle of a (possibly two-hop) MiCS gather; completion is the base handle's."""

@@ -14,7 +14,8 @@ Reference: ``deepspeed/runtime/zero/stage3.py`` (:73 optimizer, step :2040), ``p
 from __future__ import annotations
 
 import math
-from collections import OrderedDict
+from collections import OrderedDict, UserDict
+from enum import Enum
 from typing import List, Optional
 
 import torch
@@ -25,6 +26,36 @@ from ..fp16.loss_scaler import CreateLossScaler
 from .optimizer_api import ZeroOptimizerAPI
 from .partition_parameters import (Init, ZeroParamStatus, _partition_param, all_gather_params, is_zero_param, read_partition,
                                    release_partition, set_param_swapper, write_partition)
+
+
+class ZeRoTraceMode(Enum):
+    """Where the fetch-order trace stands: being recorded, complete (prefetch runs from it), or invalidated because the
+    model took another path than the recorded one."""
+    RECORD = 1
+    COMPLETE = 2
+    INVALID = 3
+
+
+class InflightParamRegistry(UserDict):
+    """Parameter -> handle of its gather in flight; only INFLIGHT parameters may be entered, and only once."""
+
+    def __setitem__(self, param, handle) -> None:
+        if param in self.data:
+            raise RuntimeError(f"{param.ds_summary()} already in registry")
+        if param.ds_status != ZeroParamStatus.INFLIGHT:
+            raise RuntimeError(f"attempted to add non-inflight parameter to registry {param.ds_summary()}")
+        self.data[param] = handle
+
+
+def get_all_parameters(sub_module: torch.nn.Module, recurse: bool = False):
+    """(name, parameter) of a module's own parameters followed by the external ones registered on it."""
+    import itertools
+    ext = getattr(sub_module, "_external_params", {})
+    return itertools.chain(sub_module.named_parameters(recurse=recurse), ((f"external_{i}", p) for i, p in enumerate(ext.values())))
+
+
+def iter_params(module: torch.nn.Module, recurse: bool = False):
+    return (p for _, p in get_all_parameters(module, recurse))
 
 
 FWD_MODULE_STACK: list = []      # modules whose forward is running (innermost last), kept by the stage-3 hooks
@@ -285,6 +316,21 @@ class DeepSpeedZeRoOffload:
 
     def get_param_coordinator(self, training=True):
         return self
+
+    # ---- trace state under the coordinator's names (ref: partitioned_param_coordinator.py:43-50, 150-175) -------------
+    def get_trace_mode(self) -> ZeRoTraceMode:
+        if self.trace_complete:
+            return ZeRoTraceMode.COMPLETE
+        return ZeRoTraceMode.INVALID if self.stats.get("trace_invalidations", 0) and not self._recording else ZeRoTraceMode.RECORD
+
+    def is_complete_trace(self) -> bool:
+        return self.get_trace_mode() == ZeRoTraceMode.COMPLETE
+
+    def is_record_trace(self) -> bool:
+        return self.get_trace_mode() == ZeRoTraceMode.RECORD
+
+    def is_invalid_trace(self) -> bool:
+        return self.get_trace_mode() == ZeRoTraceMode.INVALID
 
     # ---- the reference's public names for the same steps (parameter_offload.py:200-520) --------------------------------
     def setup_zero_stage3_hooks(self) -> None:

@@ -900,3 +900,19 @@ def runtime_utils_worker(rank, world):
     ds.comm.broadcast_object_list(objs, src=0)
     out["obj"] = objs[0]
     return out
+
+
+def mics_hierarchy_worker(rank, world):
+    """MiCS groups for a shard group spanning two 'nodes' of two ranks, and the two-hop all-gather in rank order."""
+    os.environ["HDS_MICS_NODE_SIZE"] = "2"
+    import hcache_deepspeed_b200 as ds
+    from hcache_deepspeed_b200.runtime.zero import mics
+    ds.init_distributed(dist_backend="gloo")
+    g = mics.create_mics_comm_groups(4, hierarchical_allgather=True)
+    flat = mics.create_mics_comm_groups(4, hierarchical_allgather=False)
+    local = torch.tensor([10.0 * rank, 10.0 * rank + 1])
+    two_hop = mics.hierarchical_all_gather(local, g)
+    one_hop = mics.hierarchical_all_gather(local, flat)
+    return {"hier": mics.has_hierarchical_all_gather_groups(g), "flat": mics.has_hierarchical_all_gather_groups(flat),
+            "two_hop": two_hop.tolist(), "one_hop": one_hop.tolist(),
+            "intra": ds.comm.get_world_size(group=g.param_intra_node_group), "inter": ds.comm.get_world_size(group=g.param_inter_node_shard_group)}

@@ -847,3 +847,11 @@ def test_zero3_detects_external_parameters_automatically():
     w = e3.module.emb.weight
     assert id(w) in getattr(e3.module.head, "_external_params", {})
     assert w.ds_status == ZeroParamStatus.NOT_AVAILABLE      # released again after the step
+
+
+def test_mics_hierarchical_all_gather_4ranks():
+    from tests.runtime_helper import mics_hierarchy_worker
+    want = [v for r in range(4) for v in (10.0 * r, 10.0 * r + 1)]
+    for r in run_distributed(mics_hierarchy_worker, 4):
+        assert r["hier"] and not r["flat"] and (r["intra"], r["inter"]) == (2, 2), r
+        assert r["two_hop"] == want and r["one_hop"] == want, r
