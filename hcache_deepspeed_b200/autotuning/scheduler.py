@@ -221,3 +221,68 @@ class ResourceManager:
                 r.restore_slots()
         self.experiment_queue, self.running_experiments, self.finished_experiments = [], {}, {}
         self.exp_paths = set()
+
+
+# ---- module-level entry points of the reference's scheduler (autotuning/scheduler.py:288-430) ------------------------------
+def get_job_id() -> str:
+    """Job id given by the cluster infrastructure (DLWS / DLTS), else ``unknown-job-id``."""
+    return os.environ.get("DLWS_JOB_ID") or os.environ.get("DLTS_JOB_ID") or "unknown-job-id"
+
+
+def get_user() -> str:
+    return os.environ.get("USER", "unknown-user")
+
+
+def run_experiment(exp: Dict, reservations, user_script: str, user_args: List[str]) -> int:
+    """Run ONE experiment to completion on the reserved (host, slots) through this package's launcher - the multi-node
+    form of ``ResourceManager.run_job``: the config is written to ``<result_dir>/ds_config.json`` (with the autotuning
+    block pointing its metric file there), the launcher gets ``--include host:slots@...``, output goes to
+    ``stdout.log`` / ``stderr.log``. Returns the launcher's exit code; a non-zero code is also recorded in ``stderr.log``."""
+    include = "@".join(f"{r.node.host}:{','.join(map(str, sorted(r.slots)))}" for r in reservations)
+    os.makedirs(exp["result_dir"], exist_ok=True)
+    cfg = dict(exp["ds_config"])
+    at = dict(cfg.get("autotuning") or {})
+    at.setdefault("enabled", True)
+    at.setdefault("metric_path", os.path.join(exp["result_dir"], "metrics.json"))
+    at.setdefault("model_info_path", os.path.join(exp["result_dir"], "model_info.json"))
+    cfg["autotuning"] = at
+    cfg_path = os.path.join(exp["result_dir"], "ds_config.json")
+    with open(cfg_path, "w") as f:
+        json.dump(cfg, f)
+    with open(os.path.join(exp["result_dir"], "exp.json"), "w") as f:
+        json.dump({k: v for k, v in exp.items() if k not in ("process", "ds_config")} | {"ds_config_path": cfg_path}, f)
+    args = list(user_args)
+    if "--deepspeed_config" in args:
+        args[args.index("--deepspeed_config") + 1] = cfg_path
+    else:
+        args += ["--deepspeed_config", cfg_path]
+    cmd = [sys.executable, "-m", __package__.rsplit(".", 1)[0] + ".launcher.runner"]
+    if exp.get("hostfile"):
+        cmd += ["--hostfile", str(exp["hostfile"])]
+    cmd += ["--include", include, "--master_port", str(exp.get("master_port", 29500))] + list(exp.get("launcher_args") or [])
+    cmd += [user_script] + args
+    exp["launcher_args"] = cmd[3:cmd.index(user_script)]
+    with open(os.path.join(exp["result_dir"], "stdout.log"), "w") as out, open(os.path.join(exp["result_dir"], "stderr.log"), "w") as err:
+        proc = subprocess.Popen(cmd, stdout=out, stderr=err, start_new_session=True)
+        exp["pid"] = proc.pid
+        rc = proc.wait()
+        if rc != 0:
+            err.write(f"\\nlauncher exited with code {rc}\\n")
+    clean_up(exp, reservations)
+    return rc
+
+
+def clean_up(exp: Dict, reservations) -> None:
+    """Make sure nothing of a finished (or abandoned) experiment keeps running: the launcher was started as its own
+    session, so its whole process group - launcher, per-node launch, ranks - is signalled by id. (The reference sweeps
+    the nodes with a name-pattern kill; an id cannot hit a process that is not the experiment's.)"""
+    import signal
+    pid = exp.get("pid")
+    if not pid:
+        return
+    for sig in (signal.SIGTERM, signal.SIGKILL):
+        try:
+            os.killpg(pid, sig)
+        except (ProcessLookupError, PermissionError):
+            return
+        time.sleep(0.2)

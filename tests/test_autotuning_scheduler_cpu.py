@@ -82,3 +82,29 @@ def test_autotuning_utils_and_config():
     assert memory_to_string(3 * 2 ** 30) == "3.0 G" and number_to_string(2.5e6) == "2.5 M"
     c = get_autotuning_config({"autotuning": {"enabled": True, "metric": "latency"}})
     assert c.enabled and c.metric == "latency" and c.tuner_type == "gridsearch"
+
+
+def test_run_experiment_goes_through_the_launcher(tmp_path):
+    """``run_experiment`` (module level, ref: autotuning/scheduler.py:310): one experiment on reserved slots through this
+    package's launcher - 2 local ranks - with the metric file of the autotuning block filled by the script."""
+    import json
+    import os
+    from hcache_deepspeed_b200.autotuning.scheduler import Node, Reservation, clean_up, get_job_id, get_user, run_experiment
+    script = tmp_path / "train.py"
+    script.write_text(
+        "import argparse, json, os\n"
+        "p = argparse.ArgumentParser(); p.add_argument('--deepspeed_config'); p.add_argument('--local_rank', type=int, default=0)\n"
+        "a, _ = p.parse_known_args()\n"
+        "cfg = json.load(open(a.deepspeed_config))\n"
+        "if int(os.environ.get('RANK', 0)) == 0:\n"
+        "    json.dump({'throughput': 10.0 * cfg['train_micro_batch_size_per_gpu'], 'world': int(os.environ['WORLD_SIZE'])},\n"
+        "              open(cfg['autotuning']['metric_path'], 'w'))\n")
+    node = Node("localhost", 2)
+    res = Reservation(node, node.reserve_slots(2))
+    exp = {"exp_id": 0, "name": "e0", "result_dir": str(tmp_path / "e0"), "ds_config": {"train_micro_batch_size_per_gpu": 4},
+           "master_port": 29733}
+    assert run_experiment(exp, [res], str(script), ["--deepspeed_config", "placeholder.json"]) == 0
+    assert json.load(open(os.path.join(exp["result_dir"], "metrics.json"))) == {"throughput": 40.0, "world": 2}
+    assert exp["launcher_args"][:2] == ["--include", "localhost:0,1"] and os.path.exists(os.path.join(exp["result_dir"], "exp.json"))
+    clean_up(exp, [res])                                   # nothing left to stop: must not raise
+    assert get_job_id() and get_user()
