@@ -202,3 +202,61 @@ class FPDT_LogitsLoss(torch.nn.Module):
                                                               ignore_index=self.ignore_index, reduction="sum")
             count += int((y != self.ignore_index).sum())
         return total / max(count, 1)
+
+
+# ---- input side and small functions of the reference module (sequence/fpdt_layer.py:32, 79-130, 1044-1053) -----------------
+def _rotate_half_backward(x: torch.Tensor) -> torch.Tensor:
+    x1, x2 = x.reshape(*x.shape[:-1], 2, x.shape[-1] // 2).unbind(dim=-2)
+    return torch.cat((x2, -x1), dim=-1)
+
+
+def apply_rotary_pos_emb_backward(grad_output: torch.Tensor, freqs_cos: torch.Tensor, freqs_sin: torch.Tensor) -> torch.Tensor:
+    """Gradient of ``sequence.layer.apply_rotary_pos_emb`` with respect to its input (the rotation transposed)."""
+    rot = freqs_cos.shape[-1]
+    g, rest = grad_output[..., :rot], grad_output[..., rot:]
+    g = g * freqs_cos + _rotate_half_backward(g * freqs_sin)
+    return g if rest.shape[-1] == 0 else torch.cat((g, rest), dim=-1)
+
+
+def bias_gelu(x: torch.Tensor) -> torch.Tensor:
+    """tanh-approximated GELU (the bias has been added by the caller)."""
+    return x * 0.5 * (1.0 + torch.tanh(0.79788456 * x * (1 + 0.044715 * x * x)))
+
+
+def bias_gelu_back(g: torch.Tensor, x: torch.Tensor) -> torch.Tensor:
+    t = torch.tanh(0.79788456 * x * (1 + 0.044715 * x * x))
+    return (0.5 * x * ((1 - t * t) * (0.79788456 + 0.1070322243 * x * x)) + 0.5 * (1 + t)) * g
+
+
+class FPDT_InputConstruct(torch.nn.Module):
+    """Cuts a batch for chunked sequence parallelism with a load-balanced assignment: the sequence is split into
+    ``sp_size * chunks_per_gpu`` chunks and rank ``r`` takes chunks ``r, r + sp_size, r + 2*sp_size, ...`` - under a causal
+    mask every rank then owns early (cheap) and late (expensive) positions alike. ``generate()`` returns this rank's
+    tokens / labels / position ids, the loss mask in the re-ordered order of ALL ranks (it is applied after the logits of
+    all ranks were gathered) and the attention mask untouched."""
+
+    def __init__(self, tokens, labels, loss_mask, attention_mask, position_ids, args, sp_size: int, sp_rank: int) -> None:
+        super().__init__()
+        self.tokens, self.labels, self.loss_mask = tokens, labels, loss_mask
+        self.attention_mask, self.position_ids = attention_mask, position_ids
+        self.batch_size, self.global_seq_len = tokens.shape[0], tokens.shape[1]
+        fpdt_chunk = args.ds_sequence_parallel_fpdt_chunk_size
+        assert self.global_seq_len % sp_size == 0 and self.global_seq_len % fpdt_chunk == 0
+        self.num_chunk_per_gpu = self.global_seq_len // fpdt_chunk
+        self.local_seq_len = self.global_seq_len // sp_size
+        assert self.local_seq_len % self.num_chunk_per_gpu == 0
+        self.chunk_size = self.local_seq_len // self.num_chunk_per_gpu
+        self.sp_size, self.sp_rank, self.device = sp_size, sp_rank, tokens.device
+
+    def _order(self) -> torch.Tensor:
+        """Token indices in (rank, chunk-of-rank, position) order."""
+        chunks = torch.arange(self.global_seq_len // self.chunk_size, device=self.device)
+        by_rank = chunks.reshape(self.num_chunk_per_gpu, self.sp_size).t().reshape(-1)          # rank r: r, r+sp, ...
+        return (by_rank[:, None] * self.chunk_size + torch.arange(self.chunk_size, device=self.device)[None, :]).reshape(-1)
+
+    def generate(self):
+        order = self._order()
+        mine = order[self.local_seq_len * self.sp_rank:self.local_seq_len * (self.sp_rank + 1)]
+        pick = lambda t, idx: t[:, idx] if t is not None else None     # noqa: E731
+        return pick(self.tokens, mine), pick(self.labels, mine), pick(self.loss_mask, order), self.attention_mask, \
+            pick(self.position_ids, mine)
