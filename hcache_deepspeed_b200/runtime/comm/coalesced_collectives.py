@@ -61,3 +61,35 @@ def all_to_all_quant_reduce(tensors: List[torch.Tensor], groups: dict, bits: int
         deq = dequantize_int(rc, rp, bits, torch.float32).reshape(ws, -1)
         out.append(deq.mean(dim=0))
     return out
+
+
+def all_to_all_loco_quant_reduce(params, groups: dict, loco_param=None, bits: int = 4) -> List[torch.Tensor]:
+    """ZeRO++ qgZ with LoCo error feedback (ref: coalesced_collectives.py:81): like ``all_to_all_quant_reduce`` over the
+    gradients of ``params``, but what quantisation lost on the previous call (kept per parameter in ``p.intra_ef_buf``,
+    scaled by ``err_beta``, reset every ``reset_T`` calls) is added back before quantising. 1-D gradients and sizes the
+    exchange cannot split evenly go through the plain reduce-scatter."""
+    loco_param = loco_param or {}
+    beta, reset_t = float(loco_param.get("err_beta", 0.8)), int(loco_param.get("reset_T", 1024))
+    group = groups.get("local_0") if isinstance(groups, dict) else groups
+    ws = dist.get_world_size(group) if dist.is_initialized() else 1
+    out: List[torch.Tensor] = []
+    for p in params:
+        g = p.grad
+        if g.dim() == 1 or g.numel() % (2 * ws) != 0 or ws == 1:
+            out.append(reduce_scatter_coalesced([g], group=group)[0] if ws > 1 else g.reshape(-1).float())
+            continue
+        flat = g.reshape(-1).float()
+        pad = (-flat.numel()) % (ws * 256)
+        if pad:
+            flat = torch.cat([flat, flat.new_zeros(pad)])
+        err, age = getattr(p, "intra_ef_buf", (None, 0))
+        if err is None or age >= reset_t or err.shape != flat.shape:
+            err, age = torch.zeros_like(flat), 0
+        flat = flat + beta * err
+        codes, qp = quantize_int(flat, flat.numel() // 256, bits, symmetric=True)
+        p.intra_ef_buf = (flat - dequantize_int(codes, qp, bits, torch.float32).reshape(-1), age + 1)
+        rc, rp = torch.empty_like(codes), torch.empty_like(qp)
+        dist.all_to_all_single(rc, codes, group=group)
+        dist.all_to_all_single(rp.view(-1), qp.view(-1).contiguous(), group=group)
+        out.append(dequantize_int(rc, rp, bits, torch.float32).reshape(ws, -1).mean(dim=0))
+    return out

@@ -426,7 +426,7 @@ class DeepSpeedEngine(EngineAccessors, torch.nn.Module):
                 prefetch_bucket_size=zc.prefetch_bucket_size, max_live_parameters=zc.max_live_parameters,
                 max_reuse_distance=zc.max_reuse_distance, aio_config=self._config.aio_config,
                 offload_param_config=zc.offload_param, mpu=self.mpu, clip_grad=clip,
-                zero_quantized_weights=zc.zero_quantized_weights, zero_quantized_gradients=zc.zero_quantized_gradients,
+                zero_quantized_weights=zc.zero_quantized_weights, zero_quantized_gradients=zc.zero_quantized_gradients, zeropp_loco_param=zc.zeropp_loco_param,
                 zero_quantized_nontrainable_weights=zc.zero_quantized_nontrainable_weights,
                 gradient_predivide_factor=self.gradient_predivide_factor(), verbose=self.global_rank == 0, **extra)
         elif self.fp16_enabled():

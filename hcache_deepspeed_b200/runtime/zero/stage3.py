@@ -397,6 +397,9 @@ class DeepSpeedZeroOptimizer_Stage3(ZeroOptimizerAPI):
         self.module = module
         self.optimizer = init_optimizer
         self.zero_quantized_gradients = bool(unused.get("zero_quantized_gradients", False))
+        # ZeRO++ LoCo: error feedback on the quantised gradient exchange ({"err_beta": .., "reset_T": ..}); None = plain qgZ
+        self.zeropp_loco_param = zeropp_loco_param
+        self._loco_err = {}                                    # parameter id -> (error buffer, calls since reset)
         self.qgz_stats = {"calls": 0, "bytes_sent": 0, "bytes_unquantized": 0}
         self.param_names = param_names or {}
         self.dp_process_group = dp_process_group
@@ -499,7 +502,7 @@ class DeepSpeedZeroOptimizer_Stage3(ZeroOptimizerAPI):
                 if self.gradient_predivide_factor != 1.0:
                     buf.div_(self.gradient_predivide_factor)
                 if self.zero_quantized_gradients and psize >= 256:
-                    out = self._quantized_reduce_scatter(buf, psize, ws).to(buf.dtype)
+                    out = self._quantized_reduce_scatter(buf, psize, ws, key=p.ds_id).to(buf.dtype)
                     out.mul_(self.gradient_predivide_factor)
                 else:
                     out = torch.empty(psize, dtype=buf.dtype, device=buf.device)
@@ -514,7 +517,7 @@ class DeepSpeedZeroOptimizer_Stage3(ZeroOptimizerAPI):
                 self.grad_partitions[p.ds_id] = out.clone()
             p.grad = None
 
-    def _quantized_reduce_scatter(self, buf: torch.Tensor, psize: int, ws: int, bits: int = 8) -> torch.Tensor:
+    def _quantized_reduce_scatter(self, buf: torch.Tensor, psize: int, ws: int, bits: int = 8, key=None) -> torch.Tensor:
         """ZeRO++ qgZ on one flat group: every rank quantises the ``ws`` slices of its gradient (one scale per 256 values),
         an all-to-all delivers slice r of every rank to rank r, which dequantises and averages them (ref:
         coalesced_collectives.py all_to_all_quant_reduce; the two-hop intra / inter-node form collapses on one NVSwitch node)."""
@@ -522,7 +525,16 @@ class DeepSpeedZeroOptimizer_Stage3(ZeroOptimizerAPI):
         pp = (psize + 255) // 256 * 256
         send = torch.zeros(ws, pp, dtype=torch.float32, device=buf.device)
         send[:, :psize] = buf.view(ws, psize).float()
+        loco = self.zeropp_loco_param if key is not None else None
+        if loco:
+            # error feedback: what quantisation lost last time is (partly) added back before quantising again
+            err, age = self._loco_err.get(key, (None, 0))
+            if err is None or age >= int(loco.get("reset_T", 1024)) or err.shape != send.shape:
+                err, age = torch.zeros_like(send), 0
+            send = send + float(loco.get("err_beta", 0.8)) * err
         codes, params = quantize_int(send.reshape(-1), ws * pp // 256, bits, symmetric=True)
+        if loco:
+            self._loco_err[key] = (send - dequantize_int(codes, params, bits, torch.float32).reshape(ws, pp), age + 1)
         rc, rp = torch.empty_like(codes), torch.empty_like(params)
         dist.all_to_all_single(rc.view(-1), codes.reshape(-1).contiguous(), group=self.dp_process_group)
         dist.all_to_all_single(rp.view(-1), params.reshape(-1).contiguous(), group=self.dp_process_group)

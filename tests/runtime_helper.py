@@ -561,7 +561,7 @@ def zero3_nvme_param_worker(rank, world, device, nvme_dir):
     return out
 
 
-def zeropp_worker(rank, world, qw, qg):
+def zeropp_worker(rank, world, qw, qg, loco=None):
     """ZeRO++ on one node: int8 weight all-gather (qwZ) and quantised gradient reduce via all-to-all (qgZ). Training tracks
     the unquantised run closely; traffic accounting shows the saving."""
     import hcache_deepspeed_b200 as ds
@@ -571,6 +571,8 @@ def zeropp_worker(rank, world, qw, qg):
     cfg = {"train_micro_batch_size_per_gpu": 8, "optimizer": {"type": "AdamW", "params": {"lr": 3e-3}}, "steps_per_print": 1000,
            "zero_optimization": {"stage": 3, "stage3_param_persistence_threshold": 0, "zero_quantized_weights": qw,
                                  "zero_quantized_gradients": qg}}
+    if loco is not None:
+        cfg["zero_optimization"]["zeropp_loco_param"] = loco
     engine, _, _, _ = ds.initialize(model=model, config=cfg)
     g = torch.Generator().manual_seed(5 + rank)
     x = torch.randn(8, 64, generator=g)
@@ -582,7 +584,22 @@ def zeropp_worker(rank, world, qw, qg):
         engine.step()
         losses.append(float(loss.detach()))
     flagged = sum(1 for p in model.parameters() if getattr(p, "ds_quantized_gather", False))
-    return {"losses": losses, "flagged": flagged, "qgz": dict(engine.optimizer.qgz_stats)}
+    out = {"losses": losses, "flagged": flagged, "qgz": dict(engine.optimizer.qgz_stats)}
+    if loco is not None:
+        from hcache_deepspeed_b200.runtime.comm.coalesced_collectives import all_to_all_loco_quant_reduce
+        out["loco_buffers"] = len(engine.optimizer._loco_err)
+        out["loco_ages"] = sorted({age for _, age in engine.optimizer._loco_err.values()})
+        # the standalone form: over repeated calls on the same gradient, the error fed back makes the running mean of the
+        # results approach the true mean more closely than a single quantised exchange does
+        p = torch.nn.Parameter(torch.zeros(64, 32))
+        gen = torch.Generator().manual_seed(100 + rank)
+        p.grad = torch.randn(64, 32, generator=gen)
+        grads = [torch.randn(64, 32, generator=torch.Generator().manual_seed(100 + r)) for r in range(world)]
+        want = (sum(grads) / world).reshape(-1).chunk(world)[rank]
+        outs = [all_to_all_loco_quant_reduce([p], {"local_0": None}, {"err_beta": 1.0, "reset_T": 1000})[0][:want.numel()] for _ in range(8)]
+        out["one_shot_err"] = float((outs[0] - want).abs().mean())
+        out["fed_back_err"] = float((sum(outs) / len(outs) - want).abs().mean())
+    return out
 
 
 def partition_activations_worker(rank, world):

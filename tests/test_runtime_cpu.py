@@ -855,3 +855,13 @@ def test_mics_hierarchical_all_gather_4ranks():
     for r in run_distributed(mics_hierarchy_worker, 4):
         assert r["hier"] and not r["flat"] and (r["intra"], r["inter"]) == (2, 2), r
         assert r["two_hop"] == want and r["one_hop"] == want, r
+
+
+def test_zeropp_loco_error_feedback_2ranks():
+    """``zeropp_loco_param``: the quantised gradient exchange keeps what quantisation lost per parameter and adds it back
+    next time (ref: coalesced_collectives.py all_to_all_loco_quant_reduce, stage3 zeropp_loco_param)."""
+    from tests.runtime_helper import zeropp_worker
+    for r in run_distributed(zeropp_worker, 2, False, True, {"err_beta": 0.8, "reset_T": 16}):
+        assert r["losses"][-1] < 0.5 * r["losses"][0] and r["qgz"]["calls"] > 0, r["losses"][-1]
+        assert r["loco_buffers"] >= 2 and max(r["loco_ages"]) <= 16, r
+        assert r["fed_back_err"] < 0.5 * r["one_shot_err"], r
